@@ -1,0 +1,319 @@
+"""Synthetic scene generator and the neutral scene / dump file formats.
+
+One generator feeds both sides: the CUDA backend (through ``bradot_b200.server``)
+and the reference harness ``oracle/_ref/oracle_step`` (through the ``.bscn`` file).
+The five scenes are the ones BASELINE.json names: C1 pyramid,
+C2 spheres in a container, C3 mixed pile, C4 convex chains with pin/hinge joints,
+C5 many independent spaces.  Every scene takes a size knob so the parity tests can
+run small versions of the same layout.
+
+Shape type codes follow the reference enum PhysicsServer3D::ShapeType
+(servers/physics_server_3d.h:247-259); body modes follow BodyMode (:387-392).
+"""
+import struct
+
+import numpy as np
+
+SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONVEX = range(7)
+MODE_STATIC, MODE_KINEMATIC, MODE_RIGID, MODE_RIGID_LINEAR = range(4)
+JOINT_PIN, JOINT_HINGE = 0, 1
+
+SHAPE_DT = np.dtype([("type", "<u4"), ("p", "<f4", 4), ("vert_ofs", "<u4"), ("vert_cnt", "<u4"), ("pad", "<u4")])
+BODY_DT = np.dtype([
+    ("space", "<u4"), ("mode", "<u4"), ("shape", "<u4"), ("flags", "<u4"),
+    ("xf", "<f4", 12), ("shape_xf", "<f4", 12), ("linvel", "<f4", 3), ("angvel", "<f4", 3),
+    ("mass", "<f4"), ("friction", "<f4"), ("bounce", "<f4"), ("gravity_scale", "<f4"),
+    ("lin_damp", "<f4"), ("ang_damp", "<f4"), ("layer", "<u4"), ("mask", "<u4")])
+JOINT_DT = np.dtype([("type", "<u4"), ("body_a", "<u4"), ("body_b", "<u4"), ("flags", "<u4"),
+                     ("fa", "<f4", 12), ("fb", "<f4", 12)])
+IDENT12 = np.array([1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0], dtype=np.float32)
+
+
+class Scene:
+    """Plain-data scene: structured numpy arrays, no behaviour."""
+
+    def __init__(self, n_spaces=1, dt=1.0 / 60.0, iterations=16, name="scene"):
+        self.n_spaces = n_spaces
+        self.dt = np.float32(dt)
+        self.iterations = iterations
+        self.name = name
+        self.shapes = np.zeros(0, SHAPE_DT)
+        self.bodies = np.zeros(0, BODY_DT)
+        self.joints = np.zeros(0, JOINT_DT)
+        self.verts = np.zeros((0, 3), np.float32)
+
+    # -- builders -------------------------------------------------------------
+    def add_shape(self, type_, p=(0, 0, 0, 0), verts=None):
+        rec = np.zeros(1, SHAPE_DT)
+        rec["type"] = type_
+        pp = np.zeros(4, np.float32)
+        pp[:len(p)] = p
+        rec["p"] = pp
+        if verts is not None:
+            verts = np.asarray(verts, np.float32).reshape(-1, 3)
+            rec["vert_ofs"] = len(self.verts)
+            rec["vert_cnt"] = len(verts)
+            self.verts = np.concatenate([self.verts, verts])
+        self.shapes = np.concatenate([self.shapes, rec])
+        return len(self.shapes) - 1
+
+    def add_bodies(self, n, **fields):
+        rec = np.zeros(n, BODY_DT)
+        rec["xf"] = IDENT12
+        rec["shape_xf"] = IDENT12
+        rec["mode"] = MODE_RIGID
+        rec["flags"] = 1
+        rec["mass"] = 1.0
+        rec["friction"] = 1.0
+        rec["gravity_scale"] = 1.0
+        rec["layer"] = 1
+        rec["mask"] = 1
+        for k, v in fields.items():
+            rec[k] = v
+        first = len(self.bodies)
+        self.bodies = np.concatenate([self.bodies, rec])
+        return first
+
+    def add_joints(self, n, **fields):
+        rec = np.zeros(n, JOINT_DT)
+        rec["fa"] = IDENT12
+        rec["fb"] = IDENT12
+        for k, v in fields.items():
+            rec[k] = v
+        first = len(self.joints)
+        self.joints = np.concatenate([self.joints, rec])
+        return first
+
+    def add_static_plane(self, normal, d, space=0):
+        s = self.add_shape(SHAPE_PLANE, (normal[0], normal[1], normal[2], d))
+        return self.add_bodies(1, mode=MODE_STATIC, shape=s, space=space, mass=1.0)
+
+    # -- file I/O ---------------------------------------------------------------
+    def write(self, path):
+        hdr = struct.pack("<4sIIIIIIfI7I", b"BSCN", 1, self.n_spaces, len(self.shapes), len(self.bodies),
+                          len(self.joints), len(self.verts), float(self.dt), self.iterations, *([0] * 7))
+        with open(path, "wb") as f:
+            f.write(hdr)
+            f.write(self.shapes.tobytes())
+            f.write(self.bodies.tobytes())
+            f.write(self.joints.tobytes())
+            f.write(np.ascontiguousarray(self.verts, np.float32).tobytes())
+
+    @staticmethod
+    def read(path):
+        with open(path, "rb") as f:
+            raw = f.read()
+        magic, ver, nsp, nsh, nb, nj, nv, dt, it = struct.unpack_from("<4sIIIIIIfI", raw, 0)
+        assert magic == b"BSCN" and ver == 1
+        off = struct.calcsize("<4sIIIIIIfI7I")
+        sc = Scene(nsp, dt, it)
+        sc.shapes = np.frombuffer(raw, SHAPE_DT, nsh, off).copy()
+        off += nsh * SHAPE_DT.itemsize
+        sc.bodies = np.frombuffer(raw, BODY_DT, nb, off).copy()
+        off += nb * BODY_DT.itemsize
+        sc.joints = np.frombuffer(raw, JOINT_DT, nj, off).copy()
+        off += nj * JOINT_DT.itemsize
+        sc.verts = np.frombuffer(raw, "<f4", nv * 3, off).reshape(-1, 3).copy()
+        return sc
+
+
+def read_dump(path):
+    """Read a ``.bdmp`` written by oracle_step: {(name, step): ndarray}."""
+    out = {}
+    with open(path, "rb") as f:
+        raw = f.read()
+    assert raw[:4] == b"BDMP"
+    off = 4
+    while off < len(raw):
+        name = raw[off:off + 32].split(b"\0")[0].decode()
+        off += 32
+        step, = struct.unpack_from("<i", raw, off)
+        off += 4
+        dt = raw[off:off + 4].split(b"\0")[0].decode()
+        off += 4
+        nd, = struct.unpack_from("<I", raw, off)
+        off += 4
+        shape = struct.unpack_from("<%dQ" % nd, raw, off)
+        off += 8 * nd
+        nbytes, = struct.unpack_from("<Q", raw, off)
+        off += 8
+        arr = np.frombuffer(raw, "<" + dt, nbytes // 4, off).reshape(shape).copy()
+        off += nbytes
+        out[(name, step)] = arr
+    return out
+
+
+def _quat_to_rows(q):
+    """unit quaternions (n,4 xyzw) -> row-major 3x3 (n,9), float32."""
+    x, y, z, w = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    m = np.stack([
+        1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+        2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+        2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], axis=1)
+    return m.astype(np.float32)
+
+
+def _random_rotations(rng, n):
+    q = rng.normal(size=(n, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    return _quat_to_rows(q)
+
+
+def _container(sc, half, space=0):
+    """Floor + 4 walls as static world-boundary planes (normal points inward)."""
+    sc.add_static_plane((0, 1, 0), 0.0, space)
+    sc.add_static_plane((1, 0, 0), -half, space)
+    sc.add_static_plane((-1, 0, 0), -half, space)
+    sc.add_static_plane((0, 0, 1), -half, space)
+    sc.add_static_plane((0, 0, -1), -half, space)
+
+
+# ------------------------------------------------------------------------ C1
+def pyramid(n_boxes=1000, base=45):
+    """C1: 2-D wall pyramid of unit boxes on a static plane; no RNG."""
+    sc = Scene(name="C1_pyramid_%d" % n_boxes)
+    sc.add_static_plane((0, 1, 0), 0.0)
+    box = sc.add_shape(SHAPE_BOX, (0.5, 0.5, 0.5))
+    pos = []
+    row, y = base, 0.5 + 0.001
+    while len(pos) < n_boxes and row > 0:
+        x0 = -(row - 1) * 1.05 * 0.5
+        for i in range(row):
+            if len(pos) < n_boxes:
+                pos.append((x0 + i * 1.05, y, 0.0))
+        row -= 1
+        y += 1.0 + 0.001
+    pos = np.array(pos, np.float32)
+    xf = np.tile(IDENT12, (len(pos), 1))
+    xf[:, 9:12] = pos
+    sc.add_bodies(len(pos), shape=box, xf=xf, mass=1.0, friction=1.0)
+    return sc
+
+
+# ------------------------------------------------------------------------ C2
+def spheres_container(nx=50, ny=40, nz=50, seed=42, half=15.0):
+    """C2: spheres r=0.25 on a lattice (spacing 0.55, jitter +-0.05) falling into 5 static planes."""
+    sc = Scene(name="C2_spheres_%d" % (nx * ny * nz))
+    _container(sc, half)
+    sph = sc.add_shape(SHAPE_SPHERE, (0.25,))
+    rng = np.random.default_rng(seed)
+    gx, gy, gz = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    pos = np.stack([(gx - (nx - 1) * 0.5) * 0.55, 1.0 + gy * 0.55, (gz - (nz - 1) * 0.5) * 0.55], -1).reshape(-1, 3)
+    pos = pos + rng.uniform(-0.05, 0.05, pos.shape)
+    xf = np.tile(IDENT12, (len(pos), 1))
+    xf[:, 9:12] = pos.astype(np.float32)
+    sc.add_bodies(len(pos), shape=sph, xf=xf, mass=1.0, friction=1.0)
+    return sc
+
+
+# ------------------------------------------------------------------------ C3
+def _mixed_bodies(sc, rng, pos, space=0):
+    n = len(pos)
+    kind = np.arange(n) % 3
+    he = rng.uniform(0.2, 0.4, (n, 3)).astype(np.float32)
+    rs = rng.uniform(0.2, 0.4, n).astype(np.float32)
+    cr = rng.uniform(0.15, 0.3, n).astype(np.float32)
+    ch = rng.uniform(0.8, 1.4, n).astype(np.float32)
+    shape_ids = np.zeros(n, np.uint32)
+    mass = np.zeros(n, np.float32)
+    first_shape = len(sc.shapes)
+    rec = np.zeros(n, SHAPE_DT)
+    for i in range(n):
+        pass
+    rec["type"] = np.where(kind == 0, SHAPE_BOX, np.where(kind == 1, SHAPE_SPHERE, SHAPE_CAPSULE))
+    p = np.zeros((n, 4), np.float32)
+    p[kind == 0, :3] = he[kind == 0]
+    p[kind == 1, 0] = rs[kind == 1]
+    p[kind == 2, 0] = cr[kind == 2]
+    p[kind == 2, 1] = ch[kind == 2]
+    rec["p"] = p
+    sc.shapes = np.concatenate([sc.shapes, rec])
+    shape_ids[:] = first_shape + np.arange(n)
+    vol_box = 8 * he[:, 0] * he[:, 1] * he[:, 2]
+    vol_sph = 4.0 / 3.0 * np.pi * rs ** 3
+    vol_cap = np.pi * cr ** 2 * (ch - 2 * cr) + 4.0 / 3.0 * np.pi * cr ** 3
+    mass = np.where(kind == 0, vol_box, np.where(kind == 1, vol_sph, vol_cap)).astype(np.float32)
+    xf = np.zeros((n, 12), np.float32)
+    xf[:, :9] = _random_rotations(rng, n)
+    xf[:, 9:12] = pos.astype(np.float32)
+    return sc.add_bodies(n, shape=shape_ids, xf=xf, mass=mass, friction=1.0, space=space)
+
+
+def mixed_pile(n_side=100, seed=7, half=None, spacing=1.1):
+    """C3: box / sphere / capsule round-robin on an n^3 lattice dropped into a container."""
+    n = n_side ** 3
+    sc = Scene(name="C3_mixed_%d" % n)
+    if half is None:
+        half = max(60.0 * n_side / 100.0, n_side * spacing * 0.5 + 2.0)
+    _container(sc, half)
+    rng = np.random.default_rng(seed)
+    g = np.stack(np.meshgrid(np.arange(n_side), np.arange(n_side), np.arange(n_side), indexing="ij"), -1).reshape(-1, 3)
+    pos = np.stack([(g[:, 0] - (n_side - 1) * 0.5) * spacing, 1.0 + g[:, 1] * spacing,
+                    (g[:, 2] - (n_side - 1) * 0.5) * spacing], -1)
+    _mixed_bodies(sc, rng, pos)
+    return sc
+
+
+# ------------------------------------------------------------------------ C4
+def convex_chains(n_chains=25000, chain_len=8, n_hulls=64, seed=11):
+    """C4: convex-hull debris in chains linked alternately by pin and hinge joints."""
+    sc = Scene(name="C4_convex_%d" % (n_chains * chain_len))
+    sc.add_static_plane((0, 1, 0), 0.0)
+    rng = np.random.default_rng(seed)
+    hull_ids = []
+    for _ in range(n_hulls):
+        semi = rng.uniform(0.3, 0.6, 3)
+        d = rng.normal(size=(14, 3))
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        hull_ids.append(sc.add_shape(SHAPE_CONVEX, verts=(d * semi).astype(np.float32)))
+    hull_ids = np.array(hull_ids, np.uint32)
+    side = int(np.ceil(np.sqrt(n_chains)))
+    n = n_chains * chain_len
+    c = np.arange(n_chains)
+    cx = (c % side - (side - 1) * 0.5) * 1.6
+    cz = (c // side - (side - 1) * 0.5) * 1.6
+    k = np.arange(chain_len)
+    pos = np.zeros((n_chains, chain_len, 3))
+    pos[:, :, 0] = cx[:, None]
+    pos[:, :, 2] = cz[:, None]
+    pos[:, :, 1] = 1.0 + k[None, :] * 1.3
+    pos = pos.reshape(-1, 3)
+    xf = np.tile(IDENT12, (n, 1))
+    xf[:, 9:12] = pos.astype(np.float32)
+    shape = hull_ids[rng.integers(0, n_hulls, n)]
+    first = sc.add_bodies(n, shape=shape, xf=xf, mass=1.0, friction=1.0)
+    ja = (first + (c[:, None] * chain_len + k[None, :-1])).reshape(-1)
+    jb = ja + 1
+    nj = len(ja)
+    jt = np.tile(np.arange(chain_len - 1) % 2, n_chains).astype(np.uint32)
+    fa = np.tile(IDENT12, (nj, 1))
+    fb = np.tile(IDENT12, (nj, 1))
+    fa[:, 10] = 0.65
+    fb[:, 10] = -0.65
+    sc.add_joints(nj, type=jt, body_a=ja.astype(np.uint32), body_b=jb.astype(np.uint32), flags=1, fa=fa, fb=fb)
+    return sc
+
+
+# ------------------------------------------------------------------------ C5
+def batched_worlds(n_spaces=4096, seed0=1000, lattice=(8, 4, 8)):
+    """C5: independent spaces, each a plane + a small mixed pile."""
+    sc = Scene(n_spaces=n_spaces, name="C5_worlds_%dx%d" % (n_spaces, lattice[0] * lattice[1] * lattice[2]))
+    g = np.stack(np.meshgrid(np.arange(lattice[0]), np.arange(lattice[1]), np.arange(lattice[2]), indexing="ij"),
+                 -1).reshape(-1, 3)
+    pos = np.stack([(g[:, 0] - (lattice[0] - 1) * 0.5) * 1.1, 1.0 + g[:, 1] * 1.1,
+                    (g[:, 2] - (lattice[2] - 1) * 0.5) * 1.1], -1)
+    for s in range(n_spaces):
+        sc.add_static_plane((0, 1, 0), 0.0, space=s)
+        _mixed_bodies(sc, np.random.default_rng(seed0 + s), pos, space=s)
+    return sc
+
+
+def free_fall(n=64, seed=3):
+    """Contact-free scene: tumbling mixed bodies far apart (integration parity)."""
+    sc = Scene(name="free_fall_%d" % n)
+    rng = np.random.default_rng(seed)
+    pos = np.stack([np.arange(n) * 5.0, np.full(n, 100.0), np.zeros(n)], -1)
+    first = _mixed_bodies(sc, rng, pos)
+    sc.bodies["linvel"][first:] = rng.uniform(-2, 2, (n, 3)).astype(np.float32)
+    sc.bodies["angvel"][first:] = rng.uniform(-3, 3, (n, 3)).astype(np.float32)
+    return sc

@@ -1,0 +1,523 @@
+// oracle_step -- drives the UNMODIFIED reference 3D physics (BradotPhysicsServer3D)
+// through its public RID API on a neutral scene file and dumps per-step state.
+//
+// TEST INFRASTRUCTURE ONLY: this is the checker and the timed CPU baseline, never
+// part of the product path (bradot_b200/).  It is our own code; it includes the
+// reference's headers from /root/reference and links the reference's objects
+// (oracle/build_ref.py).  Compiled with -fno-access-control so private state of
+// BradotBodyPair3D / BVH can be READ for the dumps (no reference source is edited).
+//
+// Reference entry points exercised (relative to /root/reference):
+//   modules/bradot_physics_3d/bradot_physics_server_3d.cpp:1632  BradotPhysicsServer3D::step
+//   modules/bradot_physics_3d/bradot_step_3d.cpp:186              BradotStep3D::step
+//
+// usage: oracle_step <scene.bscn> [--steps N] [--dump out.bdmp] [--dump-from A] [--dump-every K]
+//                    [--threads T] [--warmup W] [--quiet]
+// Timing JSON goes to stdout (one line).
+
+#include "core/config/engine.h"
+#include "core/config/project_settings.h"
+#include "core/io/file_access_pack.h"
+#include "core/object/worker_thread_pool.h"
+#include "core/os/main_loop.h"
+#include "core/register_core_types.h"
+#include "core/string/translation_server.h"
+#include "drivers/unix/os_unix.h"
+#include "modules/bradot_physics_3d/bradot_body_pair_3d.h"
+#include "modules/bradot_physics_3d/bradot_broad_phase_3d_bvh.h"
+#include "modules/bradot_physics_3d/bradot_physics_server_3d.h"
+#include "modules/bradot_physics_3d/bradot_step_3d.h"
+#include "modules/bradot_physics_3d/joints/bradot_hinge_joint_3d.h"
+#include "modules/bradot_physics_3d/joints/bradot_pin_joint_3d.h"
+
+#include <unistd.h>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+class OSHeadless : public OS_Unix {
+public:
+	MainLoop *ml = nullptr;
+	void initialize() override { initialize_core(); }
+	void initialize_joypads() override {}
+	void set_main_loop(MainLoop *p) override { ml = p; }
+	void delete_main_loop() override {}
+	void finalize() override {}
+	bool _check_internal_feature_support(const String &) override { return false; }
+	MainLoop *get_main_loop() const override { return ml; }
+};
+
+// ---------------------------------------------------------------- scene file
+#pragma pack(push, 1)
+struct ScnHeader {
+	char magic[4]; // "BSCN"
+	uint32_t version; // 1
+	uint32_t n_spaces, n_shapes, n_bodies, n_joints, n_verts;
+	float dt;
+	uint32_t iterations;
+	uint32_t reserved[7];
+};
+struct ScnShape {
+	uint32_t type; // PhysicsServer3D::ShapeType
+	float p[4]; // plane: n.xyz,d | sphere: r | box: half extents | capsule: radius,height
+	uint32_t vert_ofs, vert_cnt; // convex
+	uint32_t pad;
+};
+struct ScnBody {
+	uint32_t space, mode, shape, flags; // flags bit0 can_sleep, bit1 ccd, bit2 start asleep
+	float xf[12]; // basis rows (9) + origin
+	float shape_xf[12];
+	float linvel[3], angvel[3];
+	float mass, friction, bounce, gravity_scale, lin_damp, ang_damp;
+	uint32_t layer, mask;
+};
+struct ScnJoint {
+	uint32_t type; // 0 pin, 1 hinge
+	uint32_t body_a, body_b, flags; // bit0 disable collisions between bodies
+	float fa[12], fb[12]; // pin: origin of fa/fb only; hinge: local frames
+};
+#pragma pack(pop)
+
+static Transform3D xf_from(const float *f) {
+	Transform3D t;
+	t.basis = Basis(f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7], f[8]);
+	t.origin = Vector3(f[9], f[10], f[11]);
+	return t;
+}
+
+// ---------------------------------------------------------------- dump file
+struct Dump {
+	FILE *f = nullptr;
+	void arr(const char *name, int step, const char *dtype, const std::vector<uint64_t> &shape, const void *data, size_t bytes) {
+		char nm[32];
+		memset(nm, 0, sizeof(nm));
+		snprintf(nm, sizeof(nm), "%s", name);
+		fwrite(nm, 1, 32, f);
+		int32_t st = step;
+		fwrite(&st, 4, 1, f);
+		char dt[4] = { 0, 0, 0, 0 };
+		snprintf(dt, 4, "%s", dtype);
+		fwrite(dt, 1, 4, f);
+		uint32_t nd = shape.size();
+		fwrite(&nd, 4, 1, f);
+		for (uint64_t s : shape) {
+			fwrite(&s, 8, 1, f);
+		}
+		uint64_t b = bytes;
+		fwrite(&b, 8, 1, f);
+		if (bytes) {
+			fwrite(data, 1, bytes, f);
+		}
+	}
+};
+
+static void put3(std::vector<float> &v, const Vector3 &p) {
+	v.push_back(p.x);
+	v.push_back(p.y);
+	v.push_back(p.z);
+}
+
+struct World {
+	BradotPhysicsServer3D *ps = nullptr;
+	std::vector<RID> spaces, shapes, bodies, joints;
+	std::vector<BradotBody3D *> body_ptr;
+	std::map<const BradotBody3D *, int> body_index;
+	std::vector<uint32_t> body_space;
+};
+
+#define PAIR_STRIDE 12
+#define CONTACT_STRIDE 32
+
+static void dump_step(Dump &d, World &w, int step) {
+	int nb = w.bodies.size();
+	std::vector<float> bs;
+	bs.reserve(nb * 20);
+	std::vector<float> items;
+	items.reserve(nb * 14);
+	for (int i = 0; i < nb; i++) {
+		BradotBody3D *b = w.body_ptr[i];
+		const Transform3D &t = b->get_transform();
+		for (int r = 0; r < 3; r++) {
+			put3(bs, t.basis[r]);
+		}
+		put3(bs, t.origin);
+		put3(bs, b->get_linear_velocity());
+		put3(bs, b->get_angular_velocity());
+		bs.push_back(b->is_active() ? 1.0f : 0.0f);
+		bs.push_back(b->still_time);
+		// broadphase item (shape 0)
+		const BradotCollisionObject3D::Shape &s = b->shapes[0];
+		put3(items, s.aabb_cache.position);
+		put3(items, s.aabb_cache.size);
+		BradotSpace3D *space = b->get_space();
+		BradotBroadPhase3DBVH *bp = static_cast<BradotBroadPhase3DBVH *>(space->get_broadphase());
+		uint32_t id = s.bpid - 1;
+		BVHHandle h;
+		h.set_id(id);
+		auto abb = bp->bvh.tree._nodes[0].aabb; // type only; overwritten below
+		bp->bvh.tree.item_get_ABB(h, abb);
+		put3(items, abb.min);
+		put3(items, -abb.neg_max);
+		items.push_back((float)bp->bvh.tree._pairs[id].num_pairs);
+		items.push_back((float)id);
+	}
+	d.arr("bodies", step, "f4", { (uint64_t)nb, 20 }, bs.data(), bs.size() * 4);
+	d.arr("items", step, "f4", { (uint64_t)nb, 14 }, items.data(), items.size() * 4);
+
+	// pairs: walk constraint maps, emit each BradotBodyPair3D once (from its A side)
+	std::vector<int32_t> pi;
+	std::vector<float> pf;
+	std::vector<float> cf;
+	std::map<const BradotConstraint3D *, int> pair_index;
+	for (int i = 0; i < nb; i++) {
+		BradotBody3D *b = w.body_ptr[i];
+		for (const KeyValue<BradotConstraint3D *, int> &E : b->get_constraint_map()) {
+			BradotBodyPair3D *p = dynamic_cast<BradotBodyPair3D *>(E.key);
+			if (!p || p->A != b) {
+				continue;
+			}
+			pair_index[p] = pi.size() / 4;
+			pi.push_back(w.body_index[p->A]);
+			pi.push_back(w.body_index[p->B]);
+			pi.push_back(p->contact_count);
+			pi.push_back((p->collided ? 1 : 0) | (p->collide_A ? 2 : 0) | (p->collide_B ? 4 : 0));
+			put3(pf, p->sep_axis);
+			put3(pf, p->offset_B);
+			for (int c = 0; c < 4; c++) {
+				const BradotBodyPair3D::Contact &ct = p->contacts[c];
+				size_t base = cf.size();
+				put3(cf, ct.local_A);
+				put3(cf, ct.local_B);
+				put3(cf, ct.normal);
+				cf.push_back(ct.depth);
+				cf.push_back(ct.acc_normal_impulse);
+				put3(cf, ct.acc_tangent_impulse);
+				cf.push_back(ct.acc_bias_impulse);
+				cf.push_back(ct.acc_bias_impulse_center_of_mass);
+				cf.push_back(ct.mass_normal);
+				cf.push_back(ct.bias);
+				cf.push_back(ct.bounce);
+				cf.push_back(ct.active ? 1.0f : 0.0f);
+				cf.push_back(ct.used ? 1.0f : 0.0f);
+				put3(cf, ct.rA);
+				put3(cf, ct.rB);
+				cf.push_back(c < p->contact_count ? 1.0f : 0.0f);
+				while (cf.size() - base < CONTACT_STRIDE) {
+					cf.push_back(0.0f);
+				}
+			}
+		}
+	}
+	uint64_t np = pi.size() / 4;
+	d.arr("pair_ids", step, "i4", { np, 4 }, pi.data(), pi.size() * 4);
+	d.arr("pair_f", step, "f4", { np, 6 }, pf.data(), pf.size() * 4);
+	d.arr("contacts", step, "f4", { np, 4, CONTACT_STRIDE }, cf.data(), cf.size() * 4);
+
+	// solve order actually used this step: after _pre_solve_island/_solve_island the island vectors
+	// hold the constraints that were solved, in sweep order (bradot_step_3d.cpp:121-160).
+	std::vector<int32_t> order; // (island, kind, index) kind 0 = pair (index into pair_ids), 1 = joint (index into scene joints)
+	BradotStep3D *st = w.ps->stepper;
+	// islands of all spaces are overwritten space by space; only meaningful for single-space scenes
+	if (w.spaces.size() == 1) {
+		BradotSpace3D *space = w.ps->space_owner.get_or_null(w.spaces[0]);
+		uint32_t ic = space->get_island_count();
+		std::map<const BradotConstraint3D *, int> joint_index;
+		for (size_t j = 0; j < w.joints.size(); j++) {
+			joint_index[w.ps->joint_owner.get_or_null(w.joints[j])] = j;
+		}
+		for (uint32_t i = 0; i < ic && i < st->constraint_islands.size(); i++) {
+			for (BradotConstraint3D *c : st->constraint_islands[i]) {
+				auto it = pair_index.find(c);
+				if (it != pair_index.end()) {
+					order.push_back(i);
+					order.push_back(0);
+					order.push_back(it->second);
+				} else {
+					auto jt = joint_index.find(c);
+					if (jt != joint_index.end()) {
+						order.push_back(i);
+						order.push_back(1);
+						order.push_back(jt->second);
+					}
+				}
+			}
+		}
+		int32_t stats[4] = { (int32_t)space->get_island_count(), (int32_t)space->get_active_objects(), (int32_t)space->get_collision_pairs(), 0 };
+		d.arr("stats", step, "i4", { 4 }, stats, sizeof(stats));
+	}
+	d.arr("solve_order", step, "i4", { (uint64_t)order.size() / 3, 3 }, order.data(), order.size() * 4);
+}
+
+static void dump_meshes(Dump &d, World &w) {
+	// convex hull meshes as the reference built them (ConvexHullComputer, bradot_shape_3d.cpp:1099)
+	for (size_t i = 0; i < w.shapes.size(); i++) {
+		BradotShape3D *sh = w.ps->shape_owner.get_or_null(w.shapes[i]);
+		if (sh->get_type() != PhysicsServer3D::SHAPE_CONVEX_POLYGON) {
+			continue;
+		}
+		BradotConvexPolygonShape3D *cv = static_cast<BradotConvexPolygonShape3D *>(sh);
+		const Geometry3D::MeshData &m = cv->get_mesh();
+		std::vector<float> v;
+		for (uint32_t k = 0; k < m.vertices.size(); k++) {
+			put3(v, m.vertices[k]);
+		}
+		std::vector<int32_t> e;
+		for (uint32_t k = 0; k < m.edges.size(); k++) {
+			e.push_back(m.edges[k].vertex_a);
+			e.push_back(m.edges[k].vertex_b);
+			e.push_back(m.edges[k].face_a);
+			e.push_back(m.edges[k].face_b);
+		}
+		std::vector<float> fp;
+		std::vector<int32_t> fi; // per face: start, count ; then index blob
+		std::vector<int32_t> idx;
+		for (uint32_t k = 0; k < m.faces.size(); k++) {
+			put3(fp, m.faces[k].plane.normal);
+			fp.push_back(m.faces[k].plane.d);
+			fi.push_back(idx.size());
+			fi.push_back(m.faces[k].indices.size());
+			for (uint32_t q = 0; q < m.faces[k].indices.size(); q++) {
+				idx.push_back(m.faces[k].indices[q]);
+			}
+		}
+		std::vector<int32_t> ext;
+		for (uint32_t k = 0; k < cv->extreme_vertices.size(); k++) {
+			ext.push_back(cv->extreme_vertices[k]);
+		}
+		d.arr("mesh_verts", i, "f4", { (uint64_t)m.vertices.size(), 3 }, v.data(), v.size() * 4);
+		d.arr("mesh_edges", i, "i4", { (uint64_t)m.edges.size(), 4 }, e.data(), e.size() * 4);
+		d.arr("mesh_planes", i, "f4", { (uint64_t)m.faces.size(), 4 }, fp.data(), fp.size() * 4);
+		d.arr("mesh_faces", i, "i4", { (uint64_t)m.faces.size(), 2 }, fi.data(), fi.size() * 4);
+		d.arr("mesh_index", i, "i4", { (uint64_t)idx.size() }, idx.data(), idx.size() * 4);
+		d.arr("mesh_extreme", i, "i4", { (uint64_t)ext.size() }, ext.data(), ext.size() * 4);
+	}
+	// mass properties as the reference derived them (bradot_body_3d.cpp:56-166)
+	int nb = w.bodies.size();
+	std::vector<float> mp;
+	for (int i = 0; i < nb; i++) {
+		BradotBody3D *b = w.body_ptr[i];
+		mp.push_back(b->_inv_mass);
+		put3(mp, b->_inv_inertia);
+		put3(mp, b->center_of_mass_local);
+		for (int r = 0; r < 3; r++) {
+			put3(mp, b->principal_inertia_axes_local[r]);
+		}
+	}
+	d.arr("mass_props", -1, "f4", { (uint64_t)nb, 16 }, mp.data(), mp.size() * 4);
+}
+
+int main(int argc, char **argv) {
+	if (argc < 2) {
+		fprintf(stderr, "usage: oracle_step scene.bscn [--steps N] [--dump F] [--dump-from A] [--dump-every K] [--threads T] [--warmup W]\n");
+		return 2;
+	}
+	const char *scene_path = argv[1];
+	int steps = 1, dump_from = 0, dump_every = 1, threads = -1, warmup = 0;
+	const char *dump_path = nullptr;
+	for (int i = 2; i < argc; i++) {
+		std::string a = argv[i];
+		if (a == "--steps") {
+			steps = atoi(argv[++i]);
+		} else if (a == "--dump") {
+			dump_path = argv[++i];
+		} else if (a == "--dump-from") {
+			dump_from = atoi(argv[++i]);
+		} else if (a == "--dump-every") {
+			dump_every = atoi(argv[++i]);
+		} else if (a == "--threads") {
+			threads = atoi(argv[++i]);
+		} else if (a == "--warmup") {
+			warmup = atoi(argv[++i]);
+		}
+	}
+
+	FILE *sf = fopen(scene_path, "rb");
+	if (!sf) {
+		fprintf(stderr, "cannot open %s\n", scene_path);
+		return 2;
+	}
+	ScnHeader hd;
+	if (fread(&hd, sizeof(hd), 1, sf) != 1 || memcmp(hd.magic, "BSCN", 4) != 0) {
+		fprintf(stderr, "bad scene file\n");
+		return 2;
+	}
+	std::vector<ScnShape> sshapes(hd.n_shapes);
+	std::vector<ScnBody> sbodies(hd.n_bodies);
+	std::vector<ScnJoint> sjoints(hd.n_joints);
+	std::vector<float> sverts(hd.n_verts * 3);
+	if (hd.n_shapes && fread(sshapes.data(), sizeof(ScnShape), hd.n_shapes, sf) != hd.n_shapes) return 2;
+	if (hd.n_bodies && fread(sbodies.data(), sizeof(ScnBody), hd.n_bodies, sf) != hd.n_bodies) return 2;
+	if (hd.n_joints && fread(sjoints.data(), sizeof(ScnJoint), hd.n_joints, sf) != hd.n_joints) return 2;
+	if (hd.n_verts && fread(sverts.data(), 12, hd.n_verts, sf) != hd.n_verts) return 2;
+	fclose(sf);
+
+	// ---- minimal engine bring-up (order follows Main::test_setup, main/main.cpp:705-747)
+	OSHeadless os;
+	Thread::make_main_thread();
+	set_current_thread_safe_for_nodes(true);
+	os.initialize();
+	Engine *engine = memnew(Engine);
+	register_core_types();
+	PackedData *packed_data = memnew(PackedData);
+	ProjectSettings *globals = memnew(ProjectSettings);
+	register_core_settings();
+	WorkerThreadPool::get_singleton()->init(threads, 0.3);
+	(void)engine;
+	(void)packed_data;
+	(void)globals;
+
+	World w;
+	w.ps = memnew(BradotPhysicsServer3D(false));
+	w.ps->init();
+	BradotPhysicsServer3D *ps = w.ps;
+
+	for (uint32_t i = 0; i < hd.n_spaces; i++) {
+		RID sp = ps->space_create();
+		ps->space_set_active(sp, true);
+		ps->space_set_param(sp, PhysicsServer3D::SPACE_PARAM_SOLVER_ITERATIONS, hd.iterations);
+		w.spaces.push_back(sp);
+	}
+	for (uint32_t i = 0; i < hd.n_shapes; i++) {
+		const ScnShape &s = sshapes[i];
+		RID sh;
+		switch (s.type) {
+			case PhysicsServer3D::SHAPE_WORLD_BOUNDARY:
+				sh = ps->world_boundary_shape_create();
+				ps->shape_set_data(sh, Plane(Vector3(s.p[0], s.p[1], s.p[2]), s.p[3]));
+				break;
+			case PhysicsServer3D::SHAPE_SPHERE:
+				sh = ps->sphere_shape_create();
+				ps->shape_set_data(sh, s.p[0]);
+				break;
+			case PhysicsServer3D::SHAPE_BOX:
+				sh = ps->box_shape_create();
+				ps->shape_set_data(sh, Vector3(s.p[0], s.p[1], s.p[2]));
+				break;
+			case PhysicsServer3D::SHAPE_CAPSULE: {
+				sh = ps->capsule_shape_create();
+				Dictionary dct;
+				dct["radius"] = s.p[0];
+				dct["height"] = s.p[1];
+				ps->shape_set_data(sh, dct);
+			} break;
+			case PhysicsServer3D::SHAPE_CONVEX_POLYGON: {
+				sh = ps->convex_polygon_shape_create();
+				Vector<Vector3> pts;
+				for (uint32_t k = 0; k < s.vert_cnt; k++) {
+					const float *v = &sverts[(s.vert_ofs + k) * 3];
+					pts.push_back(Vector3(v[0], v[1], v[2]));
+				}
+				ps->shape_set_data(sh, pts);
+			} break;
+			default:
+				fprintf(stderr, "unsupported shape type %u\n", s.type);
+				return 2;
+		}
+		w.shapes.push_back(sh);
+	}
+	for (uint32_t i = 0; i < hd.n_bodies; i++) {
+		const ScnBody &b = sbodies[i];
+		RID body = ps->body_create();
+		ps->body_set_mode(body, (PhysicsServer3D::BodyMode)b.mode);
+		ps->body_add_shape(body, w.shapes[b.shape], xf_from(b.shape_xf), false);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_MASS, b.mass);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_FRICTION, b.friction);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_BOUNCE, b.bounce);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_GRAVITY_SCALE, b.gravity_scale);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_LINEAR_DAMP, b.lin_damp);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_ANGULAR_DAMP, b.ang_damp);
+		ps->body_set_collision_layer(body, b.layer);
+		ps->body_set_collision_mask(body, b.mask);
+		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_TRANSFORM, xf_from(b.xf));
+		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
+		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(b.angvel[0], b.angvel[1], b.angvel[2]));
+		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, (b.flags & 1) != 0);
+		if (b.flags & 2) {
+			ps->body_set_enable_continuous_collision_detection(body, true);
+		}
+		ps->body_set_space(body, w.spaces[b.space]);
+		if (b.flags & 4) {
+			ps->body_set_state(body, PhysicsServer3D::BODY_STATE_SLEEPING, true);
+		}
+		w.bodies.push_back(body);
+		BradotBody3D *bp = ps->body_owner.get_or_null(body);
+		w.body_ptr.push_back(bp);
+		w.body_index[bp] = i;
+		w.body_space.push_back(b.space);
+	}
+	for (uint32_t i = 0; i < hd.n_joints; i++) {
+		const ScnJoint &j = sjoints[i];
+		RID jr = ps->joint_create();
+		if (j.type == 0) {
+			ps->joint_make_pin(jr, w.bodies[j.body_a], Vector3(j.fa[9], j.fa[10], j.fa[11]), w.bodies[j.body_b], Vector3(j.fb[9], j.fb[10], j.fb[11]));
+		} else {
+			ps->joint_make_hinge(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
+		}
+		if (j.flags & 1) {
+			ps->joint_disable_collisions_between_bodies(jr, true);
+		}
+		w.joints.push_back(jr);
+	}
+
+	Dump d;
+	if (dump_path) {
+		d.f = fopen(dump_path, "wb");
+		fwrite("BDMP", 1, 4, d.f);
+	}
+
+	// Step 0 dump = state after construction + mass properties (space->setup() runs inside the first step,
+	// so force it here to expose inv_mass / inertia; it is idempotent: bradot_space_3d.cpp:1178-1184).
+	for (RID sp : w.spaces) {
+		ps->space_owner.get_or_null(sp)->setup();
+	}
+	if (d.f) {
+		dump_meshes(d, w);
+		if (dump_from <= 0) {
+			dump_step(d, w, 0);
+		}
+	}
+
+	for (int s = 0; s < warmup; s++) {
+		ps->step(hd.dt);
+	}
+	double phase_us[5] = { 0, 0, 0, 0, 0 };
+	auto t0 = std::chrono::steady_clock::now();
+	for (int s = 1; s <= steps; s++) {
+		ps->step(hd.dt);
+		for (RID sp : w.spaces) {
+			BradotSpace3D *space = ps->space_owner.get_or_null(sp);
+			for (int k = 0; k < 5; k++) {
+				phase_us[k] += space->get_elapsed_time((BradotSpace3D::ElapsedTime)k);
+			}
+		}
+		if (d.f && s >= dump_from && ((s - dump_from) % dump_every) == 0) {
+			dump_step(d, w, s);
+		}
+	}
+	auto t1 = std::chrono::steady_clock::now();
+	double wall = std::chrono::duration<double>(t1 - t0).count();
+	if (d.f) {
+		fclose(d.f);
+	}
+	uint64_t active = 0;
+	for (BradotBody3D *b : w.body_ptr) {
+		if (b->get_mode() >= PhysicsServer3D::BODY_MODE_KINEMATIC) {
+			active++;
+		}
+	}
+	printf("{\"steps\": %d, \"warmup\": %d, \"wall_s\": %.6f, \"bodies\": %u, \"dynamic_bodies\": %llu, \"threads\": %d, "
+		   "\"collision_pairs\": %d, \"island_count\": %d, \"active_objects\": %d, "
+		   "\"phase_us\": {\"integrate_forces\": %.0f, \"generate_islands\": %.0f, \"setup_constraints\": %.0f, "
+		   "\"solve_constraints\": %.0f, \"integrate_velocities\": %.0f}}\n",
+			steps, warmup, wall, hd.n_bodies, (unsigned long long)active, WorkerThreadPool::get_singleton()->get_thread_count(),
+			ps->get_process_info(PhysicsServer3D::INFO_COLLISION_PAIRS), ps->get_process_info(PhysicsServer3D::INFO_ISLAND_COUNT),
+			ps->get_process_info(PhysicsServer3D::INFO_ACTIVE_OBJECTS),
+			phase_us[0], phase_us[1], phase_us[2], phase_us[3], phase_us[4]);
+	fflush(stdout);
+	// Skip the engine teardown: process exit reclaims everything and the reference's
+	// unregister path expects the full Main lifecycle.
+	_exit(0);
+}
