@@ -1,0 +1,223 @@
+// C-ABI entry points of libbradot_physics_cuda.so (include/bradot_physics_cuda.h) and the per-step
+// orchestration of the kernels.  Host code here only moves data, keeps the small host mirrors
+// (spaces, shapes, joints) and enqueues kernels: no physics arithmetic for the step runs on the CPU.
+// Set-up-time host work, as in the reference: mass properties of a new body
+// (modules/bradot_physics_3d/bradot_body_3d.cpp:56-166).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "../../include/bradot_physics_cuda.h"
+#include "bpc_internal.h"
+
+int bpc_launch_schedule(bpc_context *ctx);
+int bpc_launch_forced_schedule(bpc_context *ctx);
+
+static int fail(bpc_context *ctx, const char *msg) {
+    if (ctx) ctx->err = msg;
+    return -1;
+}
+
+extern "C" bpc_context *bpc_create(int device) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return nullptr;
+    if (cudaSetDevice(device) != cudaSuccess) return nullptr;
+    bpc_context *ctx = new bpc_context();
+    ctx->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
+    ctx->counters.reserve(CNT_N, false, 0);
+    if (!ctx->counters.p || cudaMallocHost(&ctx->h_counters, CNT_N * sizeof(uint32_t)) != cudaSuccess) {
+        delete ctx;
+        return nullptr;
+    }
+    memset(ctx->h_counters, 0, CNT_N * sizeof(uint32_t));
+    return ctx;
+}
+
+extern "C" void bpc_destroy(bpc_context *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    ctx->xf.free_(); ctx->shape_xf.free_(); ctx->vel.free_(); ctx->massw.free_(); ctx->props.free_(); ctx->forces.free_();
+    ctx->meta.free_(); ctx->shape_id.free_(); ctx->items.free_(); ctx->npairs.free_(); ctx->tree_items.free_();
+    ctx->island.free_(); ctx->island_flag.free_(); ctx->shapes.free_(); ctx->meshes.free_(); ctx->mverts.free_();
+    ctx->mplanes.free_(); ctx->medges.free_(); ctx->mfaces.free_(); ctx->mindex.free_(); ctx->d_spaces.free_();
+    ctx->keys.free_(); ctx->keys_alt.free_(); ctx->vals.free_(); ctx->vals_alt.free_(); ctx->hist.free_();
+    ctx->leaf_min.free_(); ctx->leaf_max.free_(); ctx->nodes.free_(); ctx->node_parent.free_(); ctx->node_flag.free_();
+    ctx->big_items.free_(); ctx->bounds.free_(); ctx->counters.free_(); ctx->pair_keys_raw.free_();
+    for (int b = 0; b < 2; b++) {
+        ctx->pair_keys[b].free_(); ctx->pair_hdr[b].free_(); ctx->cgeo[b].free_(); ctx->cacc[b].free_();
+    }
+    ctx->except_keys.free_(); ctx->con_list.free_(); ctx->con_color.free_(); ctx->con_sorted.free_(); ctx->con_sorted_alt.free_();
+    ctx->con_info.free_(); ctx->body_best.free_(); ctx->body_colmask.free_(); ctx->color_start.free_(); ctx->scontacts.free_();
+    ctx->forced_order.free_(); ctx->forced_level_start.free_(); ctx->forced_keys.free_(); ctx->d_joints.free_();
+    if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+    delete ctx;
+}
+
+extern "C" const char *bpc_last_error(bpc_context *ctx) { return ctx ? ctx->err.c_str() : "no context (bpc_create failed: no usable CUDA device)"; }
+
+extern "C" int bpc_set_stream(bpc_context *ctx, void *s) {
+    if (!ctx) return -1;
+    ctx->stream = (cudaStream_t)s;
+    return 0;
+}
+
+extern "C" int bpc_synchronize(bpc_context *ctx) {
+    if (!ctx) return -1;
+    BPC_CHECK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- spaces
+extern "C" int bpc_space_create(bpc_context *ctx) {
+    if (!ctx) return -1;
+    if (ctx->spaces.size() >= 65535) return fail(ctx, "too many spaces (limit 65535)");
+    ctx->spaces.push_back(SpaceParams());
+    ctx->spaces_dirty = true;
+    return (int)ctx->spaces.size() - 1;
+}
+
+extern "C" int bpc_space_set_param(bpc_context *ctx, int space, int param, float v) {
+    if (!ctx) return -1;
+    if (space < 0 || space >= (int)ctx->spaces.size()) return fail(ctx, "bpc_space_set_param: invalid space");
+    SpaceParams &s = ctx->spaces[space];
+    switch (param) {
+        case BPC_SPACE_CONTACT_RECYCLE_RADIUS: s.recycle_radius = v; break;
+        case BPC_SPACE_CONTACT_MAX_SEPARATION: s.max_separation = v; break;
+        case BPC_SPACE_CONTACT_MAX_ALLOWED_PENETRATION: s.max_penetration = v; break;
+        case BPC_SPACE_CONTACT_DEFAULT_BIAS: break; // stored but unused by the reference solver (bradot_body_pair_3d.cpp:344)
+        case BPC_SPACE_BODY_LINEAR_VELOCITY_SLEEP_THRESHOLD: s.sleep_lin = v; break;
+        case BPC_SPACE_BODY_ANGULAR_VELOCITY_SLEEP_THRESHOLD: s.sleep_ang = v; break;
+        case BPC_SPACE_BODY_TIME_TO_SLEEP: s.time_to_sleep = v; break;
+        case BPC_SPACE_SOLVER_ITERATIONS: s.iterations = (int)v; break;
+        case BPC_SPACE_GRAVITY_X: s.gravity[0] = v; break;
+        case BPC_SPACE_GRAVITY_Y: s.gravity[1] = v; break;
+        case BPC_SPACE_GRAVITY_Z: s.gravity[2] = v; break;
+        case BPC_SPACE_LINEAR_DAMP: s.lin_damp = v; break;
+        case BPC_SPACE_ANGULAR_DAMP: s.ang_damp = v; break;
+        default: return fail(ctx, "bpc_space_set_param: unknown parameter");
+    }
+    ctx->spaces_dirty = true;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- shapes
+extern "C" int bpc_shape_create(bpc_context *ctx, int type, const float p[4]) {
+    if (!ctx) return -1;
+    ShapeRec r;
+    memset(&r, 0, sizeof(r));
+    r.p = make_float4(p[0], p[1], p[2], p[3]);
+    r.meta = make_uint4((uint32_t)type, 0, 0, 0);
+    switch (type) { // local AABBs as configured by the reference's _setup()s (P3D/bradot_shape_3d.cpp:156, 302-304, 489-492, 646-650)
+        case SH_PLANE:
+            r.aabb_pos = make_float4(-1e15f, -1e15f, -1e15f, 0.f);
+            r.aabb_size = make_float4(1e15f * 2, 1e15f * 2, 1e15f * 2, 0.f);
+            break;
+        case SH_SPHERE:
+            r.aabb_pos = make_float4(-p[0], -p[0], -p[0], 0.f);
+            r.aabb_size = make_float4(p[0] * 2.0f, p[0] * 2.0f, p[0] * 2.0f, 0.f);
+            break;
+        case SH_BOX:
+            r.p = make_float4(fabsf(p[0]), fabsf(p[1]), fabsf(p[2]), 0.f);
+            r.aabb_pos = make_float4(-r.p.x, -r.p.y, -r.p.z, 0.f);
+            r.aabb_size = make_float4(r.p.x * 2.0f, r.p.y * 2.0f, r.p.z * 2.0f, 0.f);
+            break;
+        case SH_CAPSULE: // p = radius, height
+            r.aabb_pos = make_float4(-p[0], -p[1] * 0.5f, -p[0], 0.f);
+            r.aabb_size = make_float4(p[0] * 2, p[1], p[0] * 2, 0.f);
+            break;
+        default:
+            return fail(ctx, "bpc_shape_create: unsupported shape type (world boundary, sphere, box, capsule; convex via bpc_shape_create_convex)");
+    }
+    ctx->h_shapes.push_back(r);
+    ctx->shapes_dirty = true;
+    return (int)ctx->h_shapes.size() - 1;
+}
+
+extern "C" int bpc_shape_create_convex(bpc_context *ctx, const float *verts, int nv, const float *planes, const int32_t *faces, int nf,
+                                       const int32_t *indices, int ni, const int32_t *edges, int ne) {
+    if (!ctx) return -1;
+    if (nv <= 0 || nf <= 0 || !verts || !planes || !faces || !indices || (ne > 0 && !edges)) return fail(ctx, "bpc_shape_create_convex: empty mesh");
+    MeshRec m;
+    m.vert_ofs = (uint32_t)ctx->h_mverts.size();
+    m.vert_cnt = (uint32_t)nv;
+    m.face_ofs = (uint32_t)ctx->h_mplanes.size();
+    m.face_cnt = (uint32_t)nf;
+    m.edge_ofs = (uint32_t)ctx->h_medges.size();
+    m.edge_cnt = (uint32_t)ne;
+    m.index_ofs = (uint32_t)ctx->h_mindex.size();
+    m.scan_all = 1;
+    V3 mn, mx;
+    for (int i = 0; i < nv; i++) {
+        V3 v(verts[3 * i], verts[3 * i + 1], verts[3 * i + 2]);
+        ctx->h_mverts.push_back(make_float4(v.x, v.y, v.z, 0.f));
+        if (i == 0) {
+            mn = mx = v;
+        } else {
+            for (int k = 0; k < 3; k++) {
+                mn[k] = std::min(mn[k], v[k]);
+                mx[k] = std::max(mx[k], v[k]);
+            }
+        }
+    }
+    for (int i = 0; i < nf; i++) {
+        ctx->h_mplanes.push_back(make_float4(planes[4 * i], planes[4 * i + 1], planes[4 * i + 2], planes[4 * i + 3]));
+        if (faces[2 * i] < 0 || faces[2 * i] + faces[2 * i + 1] > ni) return fail(ctx, "bpc_shape_create_convex: face index range out of bounds");
+        ctx->h_mfaces.push_back(make_uint2(m.index_ofs + (uint32_t)faces[2 * i], (uint32_t)faces[2 * i + 1]));
+    }
+    for (int i = 0; i < ni; i++) {
+        if (indices[i] < 0 || indices[i] >= nv) return fail(ctx, "bpc_shape_create_convex: vertex index out of bounds");
+        ctx->h_mindex.push_back((uint32_t)indices[i]);
+    }
+    for (int i = 0; i < ne; i++) {
+        ctx->h_medges.push_back(make_uint4((uint32_t)edges[4 * i], (uint32_t)edges[4 * i + 1], (uint32_t)edges[4 * i + 2], (uint32_t)edges[4 * i + 3]));
+    }
+    ShapeRec r;
+    memset(&r, 0, sizeof(r));
+    r.meta = make_uint4(SH_CONVEX, (uint32_t)ctx->h_meshes.size(), 0, 0);
+    // AABB::expand_to keeps (position, size); rebuild the same pair (P3D/bradot_shape_3d.cpp:1107-1117)
+    r.aabb_pos = make_float4(mn.x, mn.y, mn.z, 0.f);
+    r.aabb_size = make_float4(mx.x - mn.x, mx.y - mn.y, mx.z - mn.z, 0.f);
+    ctx->h_meshes.push_back(m);
+    ctx->h_shapes.push_back(r);
+    ctx->shapes_dirty = true;
+    return (int)ctx->h_shapes.size() - 1;
+}
+
+template <typename T>
+static int upload(bpc_context *ctx, DevBuf<T> &d, const std::vector<T> &h) {
+    if (h.empty()) return 0;
+    d.reserve(h.size(), false, ctx->stream);
+    if (!d.p) return fail(ctx, "out of device memory");
+    BPC_CHECK(cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    BPC_CHECK(cudaStreamSynchronize(ctx->stream)); // the host vector may be modified right after
+    return 0;
+}
+
+int bpc_flush_tables(bpc_context *ctx) {
+    if (ctx->spaces_dirty) {
+        if (upload(ctx, ctx->d_spaces, ctx->spaces)) return -1;
+        ctx->spaces_dirty = false;
+    }
+    if (ctx->shapes_dirty) {
+        if (upload(ctx, ctx->shapes, ctx->h_shapes) || upload(ctx, ctx->meshes, ctx->h_meshes) || upload(ctx, ctx->mverts, ctx->h_mverts) ||
+            upload(ctx, ctx->mplanes, ctx->h_mplanes) || upload(ctx, ctx->medges, ctx->h_medges) || upload(ctx, ctx->mfaces, ctx->h_mfaces) ||
+            upload(ctx, ctx->mindex, ctx->h_mindex))
+            return -1;
+        ctx->shapes_dirty = false;
+    }
+    if (ctx->joints_dirty) {
+        if (upload(ctx, ctx->d_joints, ctx->h_joints)) return -1;
+        ctx->joints_dirty = false;
+    }
+    if (ctx->except_dirty) {
+        std::sort(ctx->h_except.begin(), ctx->h_except.end());
+        ctx->h_except.erase(std::unique(ctx->h_except.begin(), ctx->h_except.end()), ctx->h_except.end());
+        if (upload(ctx, ctx->except_keys, ctx->h_except)) return -1;
+        ctx->n_except = (uint32_t)ctx->h_except.size();
+        ctx->except_dirty = false;
+    }
+    return 0;
+}

@@ -1,0 +1,248 @@
+// Internal layout of the CUDA rigid-body backend: struct-of-arrays state resident in HBM.
+// Public entry points are in include/bradot_physics_cuda.h; nothing here crosses the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "bpc_math.cuh"
+
+// ---- shape / body enums: numeric values of the reference enums -------------------------------
+// servers/physics_server_3d.h:247-259 (ShapeType) and :387-392 (BodyMode)
+enum { SH_PLANE = 0, SH_RAY = 1, SH_SPHERE = 2, SH_BOX = 3, SH_CAPSULE = 4, SH_CYLINDER = 5, SH_CONVEX = 6 };
+enum { MODE_STATIC = 0, MODE_KINEMATIC = 1, MODE_RIGID = 2, MODE_RIGID_LINEAR = 3 };
+
+// body flag bits (meta.x = mode | flags << 8)
+#define BF_CAN_SLEEP 1u
+#define BF_CCD 2u
+#define BF_ACTIVE 4u
+#define BF_OMIT_FORCE 8u
+#define BF_LOCK_SHIFT 8 // 6 axis-lock bits, same order as PhysicsServer3D::BodyAxis
+
+// 64-byte records: one gather = two 32-byte sectors, all of it used.
+struct __align__(16) BodyXf {
+    float4 r0, r1, r2; // basis rows (w unused)
+    float4 o;          // origin
+};
+struct __align__(16) BodyVel {
+    float4 lin, ang;   // linear / angular velocity
+    float4 blin, bang; // bias ("split impulse") velocities
+};
+struct __align__(16) BodyMassW {
+    float4 i0, i1, i2; // world inverse inertia tensor rows; w = world-oriented centre of mass x,y,z
+    float4 m;          // inv_mass, friction, bounce, (mode|flags as bits)
+};
+struct __align__(16) BodyProps {
+    float4 com_mass;   // com_local.xyz, mass
+    float4 iinv_gs;    // principal inverse inertia xyz, gravity_scale
+    float4 a0, a1, a2; // principal axes (local) rows; w = linear_damp, angular_damp, still_time
+    float4 prev_lin, prev_ang; // velocities saved before force integration (restitution)
+    float4 pad;
+};
+struct __align__(16) BodyForces {
+    float4 force, torque, cforce, ctorque; // applied (cleared each step) and constant
+};
+struct __align__(16) ItemBox {
+    float4 cache_pos, cache_size; // exact shape AABB of the last update (aabb_cache)
+    float4 smin, smax;            // stored (expanded, hysteretic) broadphase box
+};
+struct __align__(16) ShapeRec {
+    float4 p;         // plane: n.xyz,d | sphere: r | box: half extents | capsule: radius,height
+    float4 aabb_pos;  // local AABB
+    float4 aabb_size; // .w = custom bias
+    uint4 meta;       // type, mesh index (convex), 0, 0
+};
+struct MeshRec { // convex hull, offsets into the shared pools
+    uint32_t vert_ofs, vert_cnt, face_ofs, face_cnt, edge_ofs, edge_cnt, index_ofs, scan_all;
+};
+
+// Persistent manifold: 4 contacts per pair.
+struct __align__(16) ContactGeo {
+    float4 la; // local_A.xyz, w: bit0 used
+    float4 lb; // local_B.xyz
+    float4 n;  // normal.xyz
+};
+struct __align__(16) ContactAcc {
+    float4 t_n; // acc_tangent.xyz, acc_normal
+    float4 b;   // acc_bias, acc_bias_com, 0, 0
+};
+struct __align__(16) PairHdr {
+    float4 sep; // cached separating axis xyz ; w = bits: contact_count | collided<<8 | collide_A<<9 | collide_B<<10
+};
+// Solver-facing contact written by pre_solve in sweep order.
+struct __align__(16) SolveContact {
+    float4 n_mn;   // normal, mass_normal
+    float4 ra_b;   // rA, bias
+    float4 rb_bo;  // rB, bounce
+    float4 t_n;    // acc_tangent, acc_normal
+    float4 b;      // acc_bias, acc_bias_com, friction, active(1/0)
+};
+
+template <typename T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t cap = 0;
+    void reserve(size_t n, bool keep = false, cudaStream_t st = 0);
+    void free_();
+};
+
+struct SpaceParams {
+    float gravity[3] = { 0.f, -9.80665f, 0.f }; // BradotArea3D defaults, bradot_area_3d.h:50-55
+    float lin_damp = 0.1f, ang_damp = 0.1f;
+    float sleep_lin = 0.1f, sleep_ang = 0.13962634f, time_to_sleep = 0.5f; // servers/physics_server_3d.cpp:1135-1137
+    float recycle_radius = 0.01f, max_separation = 0.05f, max_penetration = 0.01f; // :1139-1141
+    int iterations = 16;
+};
+
+struct JointRec {
+    uint32_t type, a, b, flags;
+    float fa[12], fb[12];
+};
+
+struct Stats {
+    int active_objects, collision_pairs, island_count, contact_pairs, colors, contacts, overflow, steps;
+};
+
+struct bpc_context {
+    int device = 0;
+    cudaStream_t stream = 0;
+    std::string err;
+
+    // host mirrors of small tables
+    std::vector<SpaceParams> spaces;
+    std::vector<ShapeRec> h_shapes;
+    std::vector<MeshRec> h_meshes;
+    std::vector<float4> h_mverts, h_mplanes;
+    std::vector<uint4> h_medges;
+    std::vector<uint32_t> h_mindex; // per face: [count, idx...] packed; face_ofs indexes h_mfaces
+    std::vector<uint2> h_mfaces;    // (index_ofs, count)
+    std::vector<JointRec> h_joints;
+    bool shapes_dirty = true, joints_dirty = true, spaces_dirty = true;
+    uint32_t *h_counters = nullptr; // pinned mirror of the device counters of the last step
+    uint32_t launches = 0;          // kernels launched by the current / last step
+    DevBuf<JointRec> d_joints;
+    DevBuf<uint64_t> forced_keys;
+
+    uint32_t n_bodies = 0;
+    // body SoA
+    DevBuf<BodyXf> xf, shape_xf;
+    DevBuf<BodyVel> vel;
+    DevBuf<BodyMassW> massw;
+    DevBuf<BodyProps> props;
+    DevBuf<BodyForces> forces;
+    DevBuf<uint4> meta; // mode|flags<<8, layer, mask, space
+    DevBuf<uint32_t> shape_id;
+    DevBuf<ItemBox> items;
+    DevBuf<uint32_t> npairs;   // pairs per item after the last broadphase update (drives the margin)
+    DevBuf<uint32_t> tree_items; // body ids that live in the LBVH (everything except unbounded statics)
+    uint32_t n_tree = 0;
+    DevBuf<uint32_t> island; // connected-component label per body
+    DevBuf<uint32_t> island_flag;
+    // shapes
+    DevBuf<ShapeRec> shapes;
+    DevBuf<MeshRec> meshes;
+    DevBuf<float4> mverts, mplanes;
+    DevBuf<uint4> medges;
+    DevBuf<uint2> mfaces;
+    DevBuf<uint32_t> mindex;
+    DevBuf<SpaceParams> d_spaces;
+
+    // broadphase
+    DevBuf<uint64_t> keys, keys_alt;
+    DevBuf<uint32_t> vals, vals_alt;
+    DevBuf<uint32_t> hist;
+    DevBuf<float4> leaf_min, leaf_max; // sorted leaves: min.w = item id (bits), max.w = space (bits)
+    DevBuf<float4> nodes;              // 4 float4 per internal node
+    DevBuf<uint32_t> node_parent, node_flag;
+    DevBuf<uint32_t> big_items;        // static items with unbounded boxes (planes), brute-forced
+    DevBuf<float4> bounds;             // scene bounds reduction result
+    DevBuf<uint32_t> counters;         // device counters (see CNT_*)
+    uint32_t n_big = 0;
+    bool statics_dirty = true;
+
+    // pairs (double buffered: cur = this step, old = previous step)
+    DevBuf<uint64_t> pair_keys[2], pair_keys_raw;
+    DevBuf<PairHdr> pair_hdr[2];
+    DevBuf<ContactGeo> cgeo[2];
+    DevBuf<ContactAcc> cacc[2];
+    uint32_t n_pairs[2] = { 0, 0 };
+    int cur = 0;
+    size_t pair_cap = 0;
+
+    // body pairs excepted from colliding (joint_disable_collisions_between_bodies / body_add_collision_exception)
+    DevBuf<uint64_t> except_keys;
+    std::vector<uint64_t> h_except;
+    uint32_t n_except = 0;
+    bool except_dirty = false;
+    std::vector<uint8_t> h_big;  // 1 = unbounded static item (world boundary), kept out of the LBVH
+    std::vector<uint8_t> h_mode; // host mirror of the body modes (scheduling of teacher-forced sweeps)
+
+    // constraints / solver
+    DevBuf<uint32_t> con_list, con_color, con_sorted, con_sorted_alt;
+    DevBuf<uint4> con_info; // per scheduled constraint: body a, body b, flags|count, pair index
+    DevBuf<uint64_t> body_best;
+    DevBuf<uint64_t> body_colmask;
+    DevBuf<uint32_t> color_start; // 66 entries + count
+    DevBuf<SolveContact> scontacts;
+    DevBuf<uint32_t> forced_order; // teacher-forced sweep order (pair indices), optional
+    DevBuf<uint32_t> forced_level_start;
+    uint32_t n_forced = 0, n_forced_levels = 0;
+    std::vector<uint64_t> h_forced_keys;
+    std::vector<uint32_t> h_forced_joints;
+
+    int sm_count = 148;
+    Stats stats = {};
+    uint32_t step_count = 0;
+    float last_dt = 0.f;
+};
+
+enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIVE = 4, CNT_ISLANDS = 5, CNT_CONTACTS = 6,
+       CNT_OVERFLOW = 7, CNT_ROUND = 8, CNT_N = 16 };
+
+#define BPC_CHECK(x)                                                                                  \
+    do {                                                                                              \
+        cudaError_t e_ = (x);                                                                         \
+        if (e_ != cudaSuccess) {                                                                      \
+            ctx->err = std::string(#x) + ": " + cudaGetErrorString(e_);                               \
+            return -1;                                                                                \
+        }                                                                                             \
+    } while (0)
+
+template <typename T>
+void DevBuf<T>::reserve(size_t n, bool keep, cudaStream_t st) {
+    if (n <= cap) return;
+    size_t ncap = n + n / 4 + 256;
+    T *np = nullptr;
+    if (cudaMalloc(&np, ncap * sizeof(T)) != cudaSuccess) {
+        return;
+    }
+    cudaMemsetAsync(np, 0, ncap * sizeof(T), st);
+    if (keep && p && cap) cudaMemcpyAsync(np, p, cap * sizeof(T), cudaMemcpyDeviceToDevice, st);
+    if (p) {
+        cudaStreamSynchronize(st);
+        cudaFree(p);
+    }
+    p = np;
+    cap = ncap;
+}
+template <typename T>
+void DevBuf<T>::free_() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+}
+
+// ---- kernel launchers (one per .cu file) ------------------------------------------------------
+int bpc_launch_integrate_forces(bpc_context *ctx, float dt);
+int bpc_launch_integrate_velocities(bpc_context *ctx, float dt);
+int bpc_launch_refresh_bodies(bpc_context *ctx, uint32_t first, uint32_t n, int passes);
+int bpc_launch_broadphase(bpc_context *ctx);
+int bpc_launch_islands(bpc_context *ctx);
+int bpc_launch_narrowphase(bpc_context *ctx);
+int bpc_launch_solver(bpc_context *ctx, float dt);
+int bpc_launch_sleep(bpc_context *ctx, float dt);
+// radix sort of 64-bit keys (+ optional 32-bit values) on the 8-bit digits that intersect `bitmask`;
+// result is left in *keys/*vals (the pointers are swapped with their alternates as needed)
+int bpc_radix_sort(bpc_context *ctx, uint64_t **keys, uint64_t **keys_alt, uint32_t **vals, uint32_t **vals_alt, uint32_t n, uint64_t bitmask);

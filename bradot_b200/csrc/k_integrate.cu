@@ -1,0 +1,304 @@
+// Force integration, velocity/position integration, transform-dependent mass data,
+// shape AABB + hysteretic broadphase box, and the sleep test.  One thread per body; every
+// record is a 64-byte float4 struct so each warp request is fully used sectors.
+//
+// Reference semantics restated (files relative to modules/bradot_physics_3d/):
+//   bradot_body_3d.cpp:477-672   BradotBody3D::integrate_forces
+//   bradot_body_3d.cpp:674-738   BradotBody3D::integrate_velocities
+//   bradot_body_3d.cpp:44-54     BradotBody3D::_update_transform_dependent
+//   bradot_collision_object_3d.cpp:156-184  _update_shapes (AABB with 5 % feedback growth)
+//   core/math/bvh_public.inc:101-188, 473-499 ; core/math/bvh_pair.inc:66-71  item_move hysteresis
+//   bradot_body_3d.cpp:783-800 ; bradot_step_3d.cpp:162-184  sleep_test / _check_suspend
+#include "bpc_internal.h"
+
+#define IT_THREADS 128
+
+__device__ __forceinline__ M3 load_basis(const BodyXf &x) { return M3(f4v(x.r0), f4v(x.r1), f4v(x.r2)); }
+
+__global__ void __launch_bounds__(IT_THREADS) k_integrate_forces(uint32_t n, float dt, BodyVel *__restrict__ vel,
+                                                                 BodyProps *__restrict__ props, BodyForces *__restrict__ forces,
+                                                                 const BodyMassW *__restrict__ massw, const uint4 *__restrict__ meta,
+                                                                 const SpaceParams *__restrict__ spaces, uint32_t *__restrict__ counters) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool act = false;
+    if (i < n) {
+        uint4 mt = meta[i];
+        uint32_t mode = mt.x & 0xffu, flags = mt.x >> 8;
+        act = mode != MODE_STATIC && (flags & BF_ACTIVE);
+        if (act) {
+            BodyVel v = vel[i];
+            BodyProps p = props[i];
+            const SpaceParams sp = spaces[mt.w];
+            p.prev_lin = v.lin;
+            p.prev_ang = v.ang;
+            if (mode >= MODE_RIGID && !(flags & BF_OMIT_FORCE)) {
+                BodyForces f = forces[i];
+                BodyMassW mw = massw[i];
+                V3 gravity = V3(sp.gravity[0], sp.gravity[1], sp.gravity[2]) * p.iinv_gs.w;
+                float ld = sp.lin_damp + p.a0.w; // BODY_DAMP_MODE_COMBINE
+                float ad = sp.ang_damp + p.a1.w;
+                V3 force = gravity * p.com_mass.w + f4v(f.force) + f4v(f.cforce);
+                V3 torque = f4v(f.torque) + f4v(f.ctorque);
+                float damp = 1.0f - dt * ld;
+                if (damp < 0.f) damp = 0.f;
+                float adamp = 1.0f - dt * ad;
+                if (adamp < 0.f) adamp = 0.f;
+                V3 lv = f4v(v.lin) * damp;
+                V3 av = f4v(v.ang) * adamp;
+                lv += (force * mw.m.x) * dt;
+                M3 iinv(f4v(mw.i0), f4v(mw.i1), f4v(mw.i2));
+                av += xform(iinv, torque) * dt;
+                v.lin = v4(lv, 0.f);
+                v.ang = v4(av, 0.f);
+                if (f.force.x != 0.f || f.force.y != 0.f || f.force.z != 0.f || f.torque.x != 0.f || f.torque.y != 0.f || f.torque.z != 0.f) {
+                    f.force = make_float4(0.f, 0.f, 0.f, 0.f);
+                    f.torque = make_float4(0.f, 0.f, 0.f, 0.f);
+                    forces[i] = f;
+                }
+            }
+            v.blin = make_float4(0.f, 0.f, 0.f, 0.f);
+            v.bang = make_float4(0.f, 0.f, 0.f, 0.f);
+            vel[i] = v;
+            props[i].prev_lin = p.prev_lin;
+            props[i].prev_ang = p.prev_ang;
+        }
+    }
+    uint32_t m = __ballot_sync(0xffffffffu, act);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(&counters[CNT_ACTIVE], __popc(m));
+}
+
+// World-space mass data from the transform (bradot_body_3d.cpp:44-54).
+__device__ __forceinline__ void transform_dependent(const M3 &B, const BodyProps &p, uint32_t mode, BodyMassW &mw) {
+    V3 com = xform(B, f4v(p.com_mass));
+    M3 iinv = m3_zero();
+    if (mode == MODE_RIGID) {
+        M3 tb = B * M3(f4v(p.a0), f4v(p.a1), f4v(p.a2));
+        M3 tbt = transposed(tb);
+        V3 ii = f4v(p.iinv_gs);
+        M3 diag(V3(ii.x, 0.f, 0.f), V3(0.f, ii.y, 0.f), V3(0.f, 0.f, ii.z));
+        iinv = tb * diag * tbt;
+    }
+    mw.i0 = v4(iinv.r[0], com.x);
+    mw.i1 = v4(iinv.r[1], com.y);
+    mw.i2 = v4(iinv.r[2], com.z);
+}
+
+// Shape AABB + stored broadphase box.  `init` = item creation: the stored box is the exact one
+// (core/math/bvh_public.inc:2-20 "we do not expand the AABB for the first create").
+__device__ __forceinline__ void update_item(const X3 &body, const BodyXf &sx, const ShapeRec &sh, ItemBox &it, int np, bool init) {
+    X3 local(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+    X3 X = body * local;
+    Box3 la;
+    la.pos = f4v(sh.aabb_pos);
+    la.size = f4v(sh.aabb_size);
+    Box3 box = xform_aabb(X, la);
+    // (size.x + size.y) * 0.5 * 0.05 is evaluated in double in the reference (literal doubles)
+    float g = (float)((double)(it.cache_size.x + it.cache_size.y) * 0.5 * 0.05);
+    box = grow_by(box, g);
+    it.cache_pos = v4(box.pos, 0.f);
+    it.cache_size = v4(box.size, 0.f);
+    V3 bmin = box.pos, bmax = box.pos + box.size;
+    if (init) {
+        it.smin = v4(bmin, 0.f);
+        it.smax = v4(bmax, 0.f);
+        return;
+    }
+    // margin = 0.1 * (1 - min(num_pairs / 9, 1))      core/math/bvh_pair.inc:66-71
+    float x = (float)((double)(float)np * (1.0 / 9.0));
+    x = (float)(((double)x < 1.0) ? (double)x : 1.0);
+    x = (float)(1.0 - (double)x);
+    float margin = 0.1f * x;
+    // expanded_aabb_encloses_not_shrink on the stored box converted back to (position, size)
+    V3 smin = f4v(it.smin), smax = f4v(it.smax);
+    V3 ssize = smax - smin;
+    V3 src_max = smin + ssize;
+    V3 dst_max = box.pos + box.size;
+    bool enc = (smin.x <= box.pos.x) && (src_max.x >= dst_max.x) && (smin.y <= box.pos.y) && (src_max.y >= dst_max.y) &&
+               (smin.z <= box.pos.z) && (src_max.z >= dst_max.z);
+    bool keep = false;
+    if (enc) {
+        float exp_l = 0.f, new_l = 0.f;
+        exp_l += ssize.x; exp_l += ssize.y; exp_l += ssize.z;
+        new_l += box.size.x; new_l += box.size.y; new_l += box.size.z;
+        const float thr = (float)((double)0.1f * 3 * 2.0 * 1.1); // bvh_public.inc:465-470
+        keep = (exp_l - new_l) < thr;
+    }
+    if (!keep) {
+        it.smin = v4(V3(bmin.x - margin, bmin.y - margin, bmin.z - margin), 0.f);
+        // neg_max = -(max) - margin  ->  max' = -(neg_max)
+        it.smax = v4(V3(-((-bmax.x) - margin), -((-bmax.y) - margin), -((-bmax.z) - margin)), 0.f);
+    }
+}
+
+__global__ void __launch_bounds__(IT_THREADS) k_integrate_velocities(uint32_t n, float dt, BodyXf *__restrict__ xf,
+                                                                     BodyVel *__restrict__ vel, BodyMassW *__restrict__ massw,
+                                                                     const BodyProps *__restrict__ props, const uint4 *__restrict__ meta,
+                                                                     const BodyXf *__restrict__ shape_xf, const uint32_t *__restrict__ shape_id,
+                                                                     const ShapeRec *__restrict__ shapes, ItemBox *__restrict__ items,
+                                                                     const uint32_t *__restrict__ npairs) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint4 mt = meta[i];
+    uint32_t mode = mt.x & 0xffu, flags = mt.x >> 8;
+    if (mode < MODE_RIGID || !(flags & BF_ACTIVE)) return; // kinematic motion is applied by the host-side setter
+    BodyVel v = vel[i];
+    uint32_t locks = (flags >> BF_LOCK_SHIFT) & 63u;
+    if (locks) {
+        for (int k = 0; k < 3; k++) {
+            if (locks & (1u << k)) {
+                (&v.lin.x)[k] = 0.f;
+                (&v.blin.x)[k] = 0.f;
+            }
+            if (locks & (1u << (k + 3))) {
+                (&v.ang.x)[k] = 0.f;
+                (&v.bang.x)[k] = 0.f;
+            }
+        }
+        vel[i] = v;
+    }
+    BodyXf x = xf[i];
+    BodyProps p = props[i];
+    M3 B = load_basis(x);
+    V3 o = f4v(x.o);
+    V3 tw = f4v(v.ang) + f4v(v.bang);
+    float ang = length(tw);
+    if (!is_zero_approx(ang)) {
+        V3 axis = tw / ang;
+        M3 rot = m3_axis_angle(axis, ang * dt);
+        M3 ident;
+        o += xform((ident - rot) * B, f4v(p.com_mass));
+        B = rot * B;
+        B = orthonormalized(B);
+    }
+    V3 tl = f4v(v.lin) + f4v(v.blin);
+    o += tl * dt;
+    x.r0 = v4(B.r[0], 0.f);
+    x.r1 = v4(B.r[1], 0.f);
+    x.r2 = v4(B.r[2], 0.f);
+    x.o = v4(o, 0.f);
+    xf[i] = x;
+    BodyMassW mw = massw[i];
+    transform_dependent(B, p, mode, mw);
+    massw[i] = mw;
+    ItemBox it = items[i];
+    update_item(X3(B, o), shape_xf[i], shapes[shape_id[i]], it, (int)npairs[i], false);
+    items[i] = it;
+}
+
+// Body creation / teleport: derive world mass data and the broadphase item from the transform.
+__global__ void __launch_bounds__(IT_THREADS) k_refresh_bodies(uint32_t first, uint32_t n, int pass, const BodyXf *__restrict__ xf,
+                                                               BodyMassW *__restrict__ massw, const BodyProps *__restrict__ props,
+                                                               const uint4 *__restrict__ meta, const BodyXf *__restrict__ shape_xf,
+                                                               const uint32_t *__restrict__ shape_id, const ShapeRec *__restrict__ shapes,
+                                                               ItemBox *__restrict__ items) {
+    uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= first + n) return;
+    uint4 mt = meta[i];
+    uint32_t mode = mt.x & 0xffu;
+    BodyXf x = xf[i];
+    M3 B = load_basis(x);
+    BodyMassW mw = massw[i];
+    transform_dependent(B, props[i], mode, mw);
+    massw[i] = mw;
+    if (pass < 0) return; // mass data only
+    ItemBox it = items[i];
+    if (pass == 0) {
+        it.cache_pos = make_float4(0.f, 0.f, 0.f, 0.f);
+        it.cache_size = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    update_item(X3(B, f4v(x.o)), shape_xf[i], shapes[shape_id[i]], it, 0, pass == 0);
+    items[i] = it;
+}
+
+// ---- sleep: per island "all sleepy" (bradot_step_3d.cpp:162-184) ------------------------------
+__global__ void __launch_bounds__(IT_THREADS) k_sleep_test(uint32_t n, float dt, const BodyVel *__restrict__ vel, BodyProps *__restrict__ props,
+                                                           const uint4 *__restrict__ meta, const SpaceParams *__restrict__ spaces,
+                                                           const uint32_t *__restrict__ island, uint32_t *__restrict__ island_flag) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint4 mt = meta[i];
+    uint32_t mode = mt.x & 0xffu, flags = mt.x >> 8;
+    if (mode < MODE_RIGID) return;
+    uint32_t root = island[i];
+    if (!(island_flag[root] & 1u)) return; // island not stepped this frame (all members asleep)
+    bool sleepy;
+    if (!(flags & BF_CAN_SLEEP)) {
+        sleepy = false;
+    } else {
+        const SpaceParams sp = spaces[mt.w];
+        BodyVel v = vel[i];
+        float st = props[i].a2.w;
+        if (fabsf(length(f4v(v.ang))) < sp.sleep_ang && fabsf(length_squared(f4v(v.lin))) < sp.sleep_lin * sp.sleep_lin) {
+            st += dt;
+            sleepy = st > sp.time_to_sleep;
+        } else {
+            st = 0.f;
+            sleepy = false;
+        }
+        props[i].a2.w = st;
+    }
+    if (!sleepy) atomicOr(&island_flag[root], 2u); // someone is awake
+}
+
+__global__ void __launch_bounds__(IT_THREADS) k_sleep_apply(uint32_t n, uint4 *__restrict__ meta, const uint32_t *__restrict__ island,
+                                                            const uint32_t *__restrict__ island_flag) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint4 mt = meta[i];
+    uint32_t mode = mt.x & 0xffu;
+    if (mode < MODE_RIGID) return;
+    uint32_t f = island_flag[island[i]];
+    if (!(f & 1u)) return;
+    bool can_sleep = !(f & 2u);
+    bool active = (mt.x >> 8) & BF_ACTIVE;
+    if (active == can_sleep) {
+        mt.x = can_sleep ? (mt.x & ~(BF_ACTIVE << 8)) : (mt.x | (BF_ACTIVE << 8));
+        meta[i] = mt;
+    }
+}
+
+static inline uint32_t nblk(uint32_t n, uint32_t t) { return (n + t - 1) / t; }
+
+int bpc_launch_integrate_forces(bpc_context *ctx, float dt) {
+    uint32_t n = ctx->n_bodies;
+    if (!n) return 0;
+    k_integrate_forces<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->vel.p, ctx->props.p, ctx->forces.p, ctx->massw.p,
+                                                                            ctx->meta.p, ctx->d_spaces.p, ctx->counters.p);
+    BPC_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int bpc_launch_integrate_velocities(bpc_context *ctx, float dt) {
+    uint32_t n = ctx->n_bodies;
+    if (!n) return 0;
+    k_integrate_velocities<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->xf.p, ctx->vel.p, ctx->massw.p, ctx->props.p,
+                                                                                ctx->meta.p, ctx->shape_xf.p, ctx->shape_id.p,
+                                                                                ctx->shapes.p, ctx->items.p, ctx->npairs.p);
+    BPC_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int bpc_launch_refresh_bodies(bpc_context *ctx, uint32_t first, uint32_t n, int passes) {
+    if (!n) return 0;
+    if (passes < 0) {
+        k_refresh_bodies<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(first, n, -1, ctx->xf.p, ctx->massw.p, ctx->props.p, ctx->meta.p,
+                                                                              ctx->shape_xf.p, ctx->shape_id.p, ctx->shapes.p, ctx->items.p);
+    }
+    for (int pass = 0; pass < passes; pass++) {
+        k_refresh_bodies<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(first, n, pass, ctx->xf.p, ctx->massw.p, ctx->props.p,
+                                                                              ctx->meta.p, ctx->shape_xf.p, ctx->shape_id.p, ctx->shapes.p,
+                                                                              ctx->items.p);
+    }
+    BPC_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int bpc_launch_sleep(bpc_context *ctx, float dt) {
+    uint32_t n = ctx->n_bodies;
+    if (!n) return 0;
+    k_sleep_test<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->vel.p, ctx->props.p, ctx->meta.p, ctx->d_spaces.p,
+                                                                      ctx->island.p, ctx->island_flag.p);
+    k_sleep_apply<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, ctx->meta.p, ctx->island.p, ctx->island_flag.p);
+    BPC_CHECK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,212 @@
+// Persistent manifold update and support-feature contact generation.
+//   modules/bradot_physics_3d/bradot_body_pair_3d.cpp:47-122   contact_added_callback (recycle / append / replace least deep)
+//   modules/bradot_physics_3d/bradot_body_pair_3d.cpp:124-163  validate_contacts
+//   modules/bradot_physics_3d/bradot_collision_solver_3d_sat.cpp:71-88    _CollectorCallback::call
+//   :93-186 point/edge generators   :286-369 face-face clipping   :552-616 dispatch by feature type
+#pragma once
+#include "np_shapes.cuh"
+
+struct Manifold {
+    V3 la[4], lb[4], n[4];
+    float4 acc_tn[4]; // tangent xyz, normal
+    float2 acc_b[4];  // bias, bias_com
+    bool used[4];
+    int count;
+    M3 bA, bB;
+    V3 offset_B;
+    float recycle2;
+};
+
+// contact_added_callback: points are relative to A's origin.
+__device__ inline void manifold_add(Manifold &m, V3 pA, V3 pB) {
+    V3 local_A = xform_inv(m.bA, pA);
+    V3 local_B = xform_inv(m.bB, pB - m.offset_B);
+    V3 normal = normalized(pA - pB);
+    for (int i = 0; i < m.count; i++) {
+        if (distance_squared(m.la[i], local_A) < m.recycle2 && distance_squared(m.lb[i], local_B) < m.recycle2) {
+            m.la[i] = local_A; // keeps the four accumulators
+            m.lb[i] = local_B;
+            m.n[i] = normal;
+            m.used[i] = true;
+            return;
+        }
+    }
+    if (m.count == 4) {
+        int least = -1;
+        float min_depth;
+        {
+            V3 gA = xform(m.bA, local_A);
+            V3 gB = xform(m.bB, local_B) + m.offset_B;
+            min_depth = dot(gA - gB, normal);
+        }
+        for (int i = 0; i < 4; i++) {
+            V3 gA = xform(m.bA, m.la[i]);
+            V3 gB = xform(m.bB, m.lb[i]) + m.offset_B;
+            float depth = dot(gA - gB, m.n[i]);
+            if (depth < min_depth) {
+                min_depth = depth;
+                least = i;
+            }
+        }
+        if (least > -1) {
+            m.la[least] = local_A;
+            m.lb[least] = local_B;
+            m.n[least] = normal;
+            m.used[least] = true;
+            m.acc_tn[least] = make_float4(0.f, 0.f, 0.f, 0.f);
+            m.acc_b[least] = make_float2(0.f, 0.f);
+        }
+        return;
+    }
+    int k = m.count++;
+    m.la[k] = local_A;
+    m.lb[k] = local_B;
+    m.n[k] = normal;
+    m.used[k] = true;
+    m.acc_tn[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    m.acc_b[k] = make_float2(0.f, 0.f);
+}
+
+__device__ inline void manifold_validate(Manifold &m, float max_sep) {
+    float max_sep2 = max_sep * max_sep;
+    for (int i = 0; i < m.count; i++) {
+        bool erase = false;
+        if (!m.used[i]) {
+            erase = true;
+        } else {
+            m.used[i] = false;
+            V3 gA = xform(m.bA, m.la[i]);
+            V3 gB = xform(m.bB, m.lb[i]) + m.offset_B;
+            V3 axis = gA - gB;
+            float depth = dot(axis, m.n[i]);
+            if (depth < -max_sep || length_squared(gB + m.n[i] * depth - gA) > max_sep2) erase = true;
+        }
+        if (erase) {
+            if ((i + 1) < m.count) {
+                int l = m.count - 1;
+                V3 t;
+                t = m.la[i]; m.la[i] = m.la[l]; m.la[l] = t;
+                t = m.lb[i]; m.lb[i] = m.lb[l]; m.lb[l] = t;
+                t = m.n[i]; m.n[i] = m.n[l]; m.n[l] = t;
+                float4 a = m.acc_tn[i]; m.acc_tn[i] = m.acc_tn[l]; m.acc_tn[l] = a;
+                float2 b = m.acc_b[i]; m.acc_b[i] = m.acc_b[l]; m.acc_b[l] = b;
+                bool u = m.used[i]; m.used[i] = m.used[l]; m.used[l] = u;
+            }
+            i--;
+            m.count--;
+        }
+    }
+}
+
+// _CollectorCallback: the normal handed to the pair callback is ignored there (it is rebuilt from
+// the two points), so only the A/B swap matters.
+struct Collector {
+    Manifold *m;
+    bool swap;
+    bool collided;
+    V3 normal;
+    V3 *prev_axis;
+    __device__ __forceinline__ void call(V3 pA, V3 pB) {
+        if (swap) manifold_add(*m, pB, pA);
+        else manifold_add(*m, pA, pB);
+    }
+};
+
+__device__ inline void gen_point_point(const V3 *A, const V3 *B, Collector &c) { c.call(A[0], B[0]); }
+__device__ inline void gen_point_edge(const V3 *A, const V3 *B, Collector &c) {
+    c.call(A[0], closest_point_to_segment_uncapped(A[0], B[0], B[1]));
+}
+__device__ inline void gen_point_face(const V3 *A, const V3 *B, Collector &c) {
+    Pl plane = pl_from_points(B[0], B[1], B[2]);
+    c.call(A[0], pl_project(plane, A[0]));
+}
+__device__ inline void sort4(float *d) {
+#define CSWAP(a, b) if (d[b] < d[a]) { float t = d[a]; d[a] = d[b]; d[b] = t; }
+    CSWAP(0, 1) CSWAP(2, 3) CSWAP(0, 2) CSWAP(1, 3) CSWAP(1, 2)
+#undef CSWAP
+}
+__device__ inline void gen_edge_edge(const V3 *A, const V3 *B, Collector &cb) {
+    V3 rel_A = A[1] - A[0];
+    V3 rel_B = B[1] - B[0];
+    V3 c = cross(cross(rel_A, rel_B), rel_B);
+    if (is_zero_approx(dot(rel_A, c))) {
+        V3 axis = normalized(rel_A);
+        V3 base_A = A[0] - axis * dot(axis, A[0]);
+        V3 base_B = B[0] - axis * dot(axis, B[0]);
+        float dvec[4] = { dot(axis, A[0]), dot(axis, A[1]), dot(axis, B[0]), dot(axis, B[1]) };
+        sort4(dvec);
+        cb.call(base_A + axis * dvec[1], base_B + axis * dvec[1]);
+        cb.call(base_A + axis * dvec[2], base_B + axis * dvec[2]);
+        return;
+    }
+    float d = (dot(c, B[0]) - dot(A[0], c)) / dot(rel_A, c);
+    if (d < 0.0f) d = 0.0f;
+    else if (d > 1.0f) d = 1.0f;
+    V3 closest_A = A[0] + rel_A * d;
+    V3 closest_B = closest_point_to_segment_uncapped(closest_A, B[0], B[1]);
+    cb.call(closest_A, closest_B);
+}
+
+#define MAX_CLIP 32
+__device__ inline void gen_face_face(const V3 *A, int nA, const V3 *B, int nB, Collector &cb) {
+    V3 buf1[MAX_CLIP], buf2[MAX_CLIP];
+    V3 *src = buf1, *dst = buf2;
+    int len = nA;
+    for (int i = 0; i < nA; i++) src[i] = A[i];
+    Pl plane_B = pl_from_points(B[0], B[1], B[2]);
+    for (int i = 0; i < nB; i++) {
+        int i_n = (i + 1) % nB;
+        V3 e0 = B[i], e1 = B[i_n];
+        V3 clip_normal = normalized(cross(e0 - e1, plane_B.n));
+        Pl clip = pl_from_normal_point(clip_normal, e0);
+        int dst_idx = 0;
+        bool edge = len == 2;
+        for (int j = 0; j < len; j++) {
+            int j_n = (j + 1) % len;
+            V3 a0 = src[j], a1 = src[j_n];
+            float dist0 = pl_distance(clip, a0);
+            float dist1 = pl_distance(clip, a1);
+            if (dist0 <= 0) {
+                if (dst_idx >= MAX_CLIP) return;
+                dst[dst_idx++] = src[j];
+            }
+            if ((dist0 * dist1) < 0 && !(edge && j)) {
+                V3 rel = a1 - a0;
+                float den = dot(clip.n, rel);
+                float dist = -(dot(clip.n, a0) - clip.d) / den;
+                V3 inters = a0 + rel * dist;
+                if (dst_idx >= MAX_CLIP) return;
+                dst[dst_idx++] = inters;
+            }
+        }
+        len = dst_idx;
+        V3 *t = src; src = dst; dst = t;
+    }
+    for (int i = 0; i < len; i++) {
+        float d = pl_distance(plane_B, src[i]);
+        V3 closest_B = src[i] - plane_B.n * d;
+        if (dot(cb.normal, src[i]) >= dot(cb.normal, closest_B)) continue;
+        cb.call(src[i], closest_B);
+    }
+}
+
+// _generate_contacts_from_supports (…sat.cpp:552-616); no circle features (cylinders are out of scope)
+__device__ inline void generate_contacts_from_supports(const V3 *pA, int nA, int tA, const V3 *pB, int nB, int tB, Collector &cb) {
+    const V3 *A = pA, *B = pB;
+    int cA = nA, cB = nB, vA = tA, vB = tB;
+    if (tA > tB) {
+        cb.swap = !cb.swap;
+        cb.normal = -cb.normal;
+        A = pB; B = pA; cA = nB; cB = nA; vA = tB; vB = tA;
+    }
+    if (vA == FEATURE_POINT) {
+        if (vB == FEATURE_POINT) gen_point_point(A, B, cb);
+        else if (vB == FEATURE_EDGE) gen_point_edge(A, B, cb);
+        else gen_point_face(A, B, cb);
+    } else if (vA == FEATURE_EDGE) {
+        if (vB == FEATURE_EDGE) gen_edge_edge(A, B, cb);
+        else gen_face_face(A, cA, B, cB, cb);
+    } else {
+        gen_face_face(A, cA, B, cB, cb);
+    }
+}

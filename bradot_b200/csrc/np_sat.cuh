@@ -1,0 +1,433 @@
+// Separating-axis narrowphase for sphere / box / capsule / convex pairs and the world-boundary
+// (plane) case, restated from the reference with the same axis order, the same early-outs and the
+// cached previous axis as first candidate.
+//   modules/bradot_physics_3d/bradot_collision_solver_3d_sat.cpp
+//     :618-767  SeparatorAxisTest (test_axis :641-691, generate_contacts :704-756)
+//     :775-824  analytic_sphere_collision     :827-906 sphere-sphere / sphere-box / sphere-capsule
+//     :957-1017 sphere-convex   :1076-1171 box-box   :1174-1270 box-capsule   :1385-1500 box-convex
+//     :1637-1666 capsule-capsule   :1694-1758 capsule-convex   :2032-2164 convex-convex (Gauss-map pruning)
+//   modules/bradot_physics_3d/bradot_collision_solver_3d.cpp:42-95  solve_static_world_boundary
+#pragma once
+#include "np_contacts.cuh"
+
+struct Separator {
+    const Sh *A, *B;
+    const X3 *xA, *xB;
+    float best_depth;
+    V3 best_axis;
+    Collector *cb;
+
+    __device__ __forceinline__ void init(const Sh *a, const X3 *xa, const Sh *b, const X3 *xb, Collector *c) {
+        A = a; B = b; xA = xa; xB = xb; cb = c;
+        best_depth = 1e15f;
+        best_axis = V3();
+    }
+    __device__ inline bool test_axis(V3 axis) {
+        if (is_zero_approx(axis)) axis = V3(0.0f, 1.0f, 0.0f);
+        float min_A = 0.f, max_A = 0.f, min_B = 0.f, max_B = 0.f;
+        project_range(*A, axis, *xA, min_A, max_A);
+        project_range(*B, axis, *xB, min_B, max_B);
+        min_B -= (max_A - min_A) * 0.5f;
+        max_B += (max_A - min_A) * 0.5f;
+        min_B -= (min_A + max_A) * 0.5f;
+        max_B -= (min_A + max_A) * 0.5f;
+        if (min_B > 0.0f || max_B < 0.0f) return false;
+        if (min_B < 0.0f) min_B = -min_B;
+        if (max_B < min_B) {
+            if (max_B < best_depth) {
+                best_depth = max_B;
+                best_axis = axis;
+            }
+        } else {
+            if (min_B < best_depth) {
+                best_depth = min_B;
+                best_axis = -axis;
+            }
+        }
+        return true;
+    }
+    __device__ __forceinline__ bool test_previous_axis() {
+        if (cb->prev_axis && !(*cb->prev_axis == V3())) return test_axis(*cb->prev_axis);
+        return true;
+    }
+    __device__ inline void generate_contacts() {
+        if (best_axis == V3(0.f, 0.f, 0.f)) return;
+        V3 sA[MAX_SUPPORTS], sB[MAX_SUPPORTS];
+        int nA, nB, tA, tB;
+        get_supports(*A, normalized(xform_inv(xA->b, -best_axis)), sA, nA, tA);
+        for (int i = 0; i < nA; i++) sA[i] = xform(*xA, sA[i]);
+        get_supports(*B, normalized(xform_inv(xB->b, best_axis)), sB, nB, tB);
+        for (int i = 0; i < nB; i++) sB[i] = xform(*xB, sB[i]);
+        cb->normal = best_axis;
+        if (cb->prev_axis) *cb->prev_axis = best_axis;
+        if (nA >= 1 && nB >= 1) generate_contacts_from_supports(sA, nA, tA, sB, nB, tB, *cb);
+        cb->collided = true;
+    }
+};
+
+__device__ inline void analytic_sphere_collision(V3 oa, float ra, V3 ob, float rb, Collector &c) {
+    V3 b_to_a = oa - ob;
+    float len = length(b_to_a);
+    float overlap = ra + rb - len;
+    if (overlap < 0) return;
+    c.collided = true;
+    if ((double)len < BPC_CMP_EPSILON) b_to_a = V3(0.f, 1.f, 0.f);
+    else b_to_a /= len;
+    if (ra < rb) {
+        V3 pa = oa - b_to_a * ra;
+        V3 pb = pa + b_to_a * overlap;
+        c.call(pa, pb);
+    } else {
+        V3 pb = ob + b_to_a * rb;
+        V3 pa = pb - b_to_a * overlap;
+        c.call(pa, pb);
+    }
+}
+
+__device__ inline void col_sphere_sphere(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    analytic_sphere_collision(xa.o, a.p.x * length(xa.b.r[0]), xb.o, b.p.x * length(xb.b.r[0]), c);
+}
+
+__device__ inline void col_sphere_box(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    V3 center = xform(affine_inverse(xb), xa.o);
+    V3 ext(b.p.x, b.p.y, b.p.z);
+    V3 nearest(fminf(fmaxf(center.x, -ext.x), ext.x), fminf(fmaxf(center.y, -ext.y), ext.y), fminf(fmaxf(center.z, -ext.z), ext.z));
+    nearest = xform(xb, nearest);
+    V3 delta = nearest - xa.o;
+    float len = length(delta);
+    float radius = a.p.x * length(xa.b.r[0]);
+    if (len > radius + 0.f + 0.f) return;
+    c.collided = true;
+    V3 axis;
+    if (len == 0) axis = normalized(xb.o - nearest);
+    else axis = delta / len;
+    V3 pa = xa.o + (radius + 0.f) * axis;
+    c.call(pa, nearest);
+}
+
+__device__ inline void col_sphere_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    float scale_A = length(xa.b.r[0]);
+    float scale_B = length(xb.b.r[0]);
+    V3 cap_axis = xb.b.col(1) * (b.p.y * 0.5f - b.p.x);
+    V3 s0 = xb.o + cap_axis, s1 = xb.o - cap_axis;
+    V3 closest = closest_point_to_segment(xa.o, s0, s1);
+    analytic_sphere_collision(xa.o, a.p.x * scale_A, closest, b.p.x * scale_B, c);
+}
+
+// geometry_3d.cpp:36-131 (David Eberly's segment-segment distance)
+__device__ inline void closest_points_between_segments(V3 p0, V3 p1, V3 q0, V3 q1, V3 &ps, V3 &qt) {
+    V3 p = p1 - p0, q = q1 - q0, r = p0 - q0;
+    float a = dot(p, p), b = dot(p, q), c = dot(q, q), d = dot(p, r), e = dot(q, r);
+    float s = 0.0f, t = 0.0f;
+    float det = a * c - b * b;
+    if ((double)det > BPC_CMP_EPSILON) {
+        float bte = b * e, ctd = c * d;
+        if (bte <= ctd) {
+            if (e <= 0.0f) {
+                s = (-d >= a ? 1 : (-d > 0.0f ? -d / a : 0.0f));
+                t = 0.0f;
+            } else if (e < c) {
+                s = 0.0f;
+                t = e / c;
+            } else {
+                s = (b - d >= a ? 1 : (b - d > 0.0f ? (b - d) / a : 0.0f));
+                t = 1;
+            }
+        } else {
+            s = bte - ctd;
+            if (s >= det) {
+                if (b + e <= 0.0f) {
+                    s = (-d <= 0.0f ? 0.0f : (-d < a ? -d / a : 1));
+                    t = 0.0f;
+                } else if (b + e < c) {
+                    s = 1;
+                    t = (b + e) / c;
+                } else {
+                    s = (b - d <= 0.0f ? 0.0f : (b - d < a ? (b - d) / a : 1));
+                    t = 1;
+                }
+            } else {
+                float ate = a * e, btd = b * d;
+                if (ate <= btd) {
+                    s = (-d <= 0.0f ? 0.0f : (-d >= a ? 1 : -d / a));
+                    t = 0.0f;
+                } else {
+                    t = ate - btd;
+                    if (t >= det) {
+                        s = (b - d <= 0.0f ? 0.0f : (b - d >= a ? 1 : (b - d) / a));
+                        t = 1;
+                    } else {
+                        s /= det;
+                        t /= det;
+                    }
+                }
+            }
+        }
+    } else {
+        if (e <= 0.0f) {
+            s = (-d <= 0.0f ? 0.0f : (-d >= a ? 1 : -d / a));
+            t = 0.0f;
+        } else if (e >= c) {
+            s = (b - d <= 0.0f ? 0.0f : (b - d >= a ? 1 : (b - d) / a));
+            t = 1;
+        } else {
+            s = 0.0f;
+            t = e / c;
+        }
+    }
+    ps = (1 - s) * p0 + s * p1;
+    qt = (1 - t) * q0 + t * q1;
+}
+
+__device__ inline void col_capsule_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    float scale_A = length(xa.b.r[0]);
+    float scale_B = length(xb.b.r[0]);
+    V3 axA = xa.b.col(1) * (a.p.y * 0.5f - a.p.x);
+    V3 axB = xb.b.col(1) * (b.p.y * 0.5f - b.p.x);
+    V3 ca, cbp;
+    closest_points_between_segments(xa.o + axA, xa.o - axA, xb.o + axB, xb.o - axB, ca, cbp);
+    analytic_sphere_collision(ca, a.p.x * scale_A, cbp, b.p.x * scale_B, c);
+}
+
+__device__ inline V3 box_corner_toward(const Sh &box, const X3 &xf, V3 cn) {
+    return xform(xf, V3((cn.x < 0) ? -box.p.x : box.p.x, (cn.y < 0) ? -box.p.y : box.p.y, (cn.z < 0) ? -box.p.z : box.p.z));
+}
+
+__device__ inline void col_box_box(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    Separator sep;
+    sep.init(&a, &xa, &b, &xb, &c);
+    if (!sep.test_previous_axis()) return;
+    for (int i = 0; i < 3; i++) {
+        if (!sep.test_axis(normalized(xa.b.col(i)))) return;
+    }
+    for (int i = 0; i < 3; i++) {
+        if (!sep.test_axis(normalized(xb.b.col(i)))) return;
+    }
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) {
+            V3 axis = cross(xa.b.col(i), xb.b.col(j));
+            if (is_zero_approx(length_squared(axis))) continue;
+            axis = normalized(axis);
+            if (!sep.test_axis(axis)) return;
+        }
+    }
+    sep.generate_contacts();
+}
+
+__device__ inline void col_box_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    Separator sep;
+    sep.init(&a, &xa, &b, &xb, &c);
+    if (!sep.test_previous_axis()) return;
+    for (int i = 0; i < 3; i++) {
+        if (!sep.test_axis(normalized(xa.b.col(i)))) return;
+    }
+    V3 cyl_axis = normalized(xb.b.col(1));
+    for (int i = 0; i < 3; i++) {
+        V3 axis = cross(xa.b.col(i), cyl_axis);
+        if (is_zero_approx(length_squared(axis))) continue;
+        if (!sep.test_axis(normalized(axis))) return;
+    }
+    for (int i = 0; i < 2; i++) {
+        for (int j = 0; j < 2; j++) {
+            for (int k = 0; k < 2; k++) {
+                V3 he(a.p.x, a.p.y, a.p.z);
+                he.x *= (i * 2 - 1);
+                he.y *= (j * 2 - 1);
+                he.z *= (k * 2 - 1);
+                V3 point = xa.o;
+                for (int l = 0; l < 3; l++) point += xa.b.col(l) * he[l];
+                Pl pl;
+                pl.n = cyl_axis;
+                pl.d = 0.f;
+                V3 axis = normalized(pl_project(pl, point));
+                if (!sep.test_axis(axis)) return;
+            }
+        }
+    }
+    for (int i = 0; i < 2; i++) {
+        V3 cap_axis = xb.b.col(1) * (b.p.y * 0.5f - b.p.x);
+        V3 sphere_pos = xb.o + ((i == 0) ? cap_axis : -cap_axis);
+        V3 cnormal = xform_inv(xa, sphere_pos);
+        V3 cpoint = box_corner_toward(a, xa, cnormal);
+        V3 point_axis = normalized(sphere_pos - cpoint);
+        if (!sep.test_axis(point_axis)) return;
+        for (int j = 0; j < 3; j++) {
+            V3 axis = normalized(cross(cross(point_axis, xa.b.col(j)), xa.b.col(j)));
+            if (!sep.test_axis(axis)) return;
+        }
+    }
+    sep.generate_contacts();
+}
+
+__device__ inline void col_sphere_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    Separator sep;
+    sep.init(&a, &xa, &b, &xb, &c);
+    if (!sep.test_previous_axis()) return;
+    const MeshView &m = b.m;
+    M3 bn = transposed(inverse(xb.b));
+    for (uint32_t i = 0; i < m.nf; i++) {
+        if (!sep.test_axis(normalized(xform(bn, f4v(__ldg(&m.planes[i])))))) return;
+    }
+    for (uint32_t i = 0; i < m.ne; i++) {
+        uint4 e = __ldg(&m.edges[i]);
+        V3 v1 = xform(xb, mv_vert(m, e.x)), v2 = xform(xb, mv_vert(m, e.y)), v3 = xa.o;
+        V3 n1 = v2 - v1, n2 = v2 - v3;
+        if (!sep.test_axis(normalized(cross(cross(n1, n2), n1)))) return;
+    }
+    for (uint32_t i = 0; i < m.nv; i++) {
+        V3 v1 = xform(xb, mv_vert(m, i));
+        if (!sep.test_axis(normalized(xa.o - v1))) return;
+    }
+    sep.generate_contacts();
+}
+
+__device__ inline void col_box_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    Separator sep;
+    sep.init(&a, &xa, &b, &xb, &c);
+    if (!sep.test_previous_axis()) return;
+    const MeshView &m = b.m;
+    for (int i = 0; i < 3; i++) {
+        if (!sep.test_axis(normalized(xa.b.col(i)))) return;
+    }
+    M3 bn = transposed(inverse(xb.b));
+    for (uint32_t i = 0; i < m.nf; i++) {
+        if (!sep.test_axis(normalized(xform(bn, f4v(__ldg(&m.planes[i])))))) return;
+    }
+    for (int i = 0; i < 3; i++) {
+        V3 e1 = xa.b.col(i);
+        for (uint32_t j = 0; j < m.ne; j++) {
+            uint4 e = __ldg(&m.edges[j]);
+            V3 e2 = xform(xb.b, mv_vert(m, e.x)) - xform(xb.b, mv_vert(m, e.y));
+            if (!sep.test_axis(normalized(cross(e1, e2)))) return;
+        }
+    }
+    sep.generate_contacts();
+}
+
+__device__ inline void col_capsule_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    Separator sep;
+    sep.init(&a, &xa, &b, &xb, &c);
+    if (!sep.test_previous_axis()) return;
+    const MeshView &m = b.m;
+    M3 bn = transposed(inverse(xb.b));
+    for (uint32_t i = 0; i < m.nf; i++) {
+        if (!sep.test_axis(normalized(xform(bn, f4v(__ldg(&m.planes[i])))))) return;
+    }
+    for (uint32_t i = 0; i < m.ne; i++) {
+        uint4 e = __ldg(&m.edges[i]);
+        V3 edge_axis = xform(xb.b, mv_vert(m, e.x)) - xform(xb.b, mv_vert(m, e.y));
+        if (!sep.test_axis(normalized(cross(edge_axis, xa.b.col(1))))) return;
+    }
+    for (int i = 0; i < 2; i++) {
+        V3 cap_axis = xa.b.col(1) * (a.p.y * 0.5f - a.p.x);
+        V3 sphere_pos = xa.o + ((i == 0) ? cap_axis : -cap_axis);
+        for (uint32_t j = 0; j < m.ne; j++) {
+            uint4 e = __ldg(&m.edges[j]);
+            V3 n1 = sphere_pos - xform(xb, mv_vert(m, e.x));
+            V3 n2 = xform(xb.b, mv_vert(m, e.x)) - xform(xb.b, mv_vert(m, e.y));
+            if (!sep.test_axis(normalized(cross(cross(n1, n2), n2)))) return;
+        }
+    }
+    sep.generate_contacts();
+}
+
+__device__ __forceinline__ bool is_minkowski_face(V3 A, V3 B, V3 B_x_A, V3 C, V3 D, V3 D_x_C) {
+    float CBA = dot(C, B_x_A), DBA = dot(D, B_x_A), ADC = dot(A, D_x_C), BDC = dot(B, D_x_C);
+    return (CBA * DBA < 0.0f) && (ADC * BDC < 0.0f) && (CBA * BDC > 0.0f);
+}
+
+__device__ inline void col_convex_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
+    Separator sep;
+    sep.init(&a, &xa, &b, &xb, &c);
+    if (!sep.test_previous_axis()) return;
+    const MeshView &ma = a.m, &mb = b.m;
+    M3 an = transposed(inverse(xa.b));
+    for (uint32_t i = 0; i < ma.nf; i++) {
+        if (!sep.test_axis(normalized(xform(an, f4v(__ldg(&ma.planes[i])))))) return;
+    }
+    M3 bn = transposed(inverse(xb.b));
+    for (uint32_t i = 0; i < mb.nf; i++) {
+        if (!sep.test_axis(normalized(xform(bn, f4v(__ldg(&mb.planes[i])))))) return;
+    }
+    for (uint32_t i = 0; i < ma.ne; i++) {
+        uint4 ea = __ldg(&ma.edges[i]);
+        V3 p1 = xform(xa, mv_vert(ma, ea.x)), q1 = xform(xa, mv_vert(ma, ea.y));
+        V3 e1 = q1 - p1;
+        V3 u1 = normalized(xform(xa.b, f4v(__ldg(&ma.planes[ea.z]))));
+        V3 v1 = normalized(xform(xa.b, f4v(__ldg(&ma.planes[ea.w]))));
+        for (uint32_t j = 0; j < mb.ne; j++) {
+            uint4 eb = __ldg(&mb.edges[j]);
+            V3 p2 = xform(xb, mv_vert(mb, eb.x)), q2 = xform(xb, mv_vert(mb, eb.y));
+            V3 e2 = q2 - p2;
+            V3 u2 = normalized(xform(xb.b, f4v(__ldg(&mb.planes[eb.z]))));
+            V3 v2 = normalized(xform(xb.b, f4v(__ldg(&mb.planes[eb.w]))));
+            if (is_minkowski_face(u1, v1, -e1, -u2, -v2, -e2)) {
+                if (!sep.test_axis(normalized(cross(e1, e2)))) return;
+            }
+        }
+    }
+    sep.generate_contacts();
+}
+
+// plane (world boundary, shape A of the call) against any supported shape
+__device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, const X3 &xb, Collector &c, bool swap_result) {
+    // Transform3D::xform(Plane): transform_3d.h:154-158, 241-252
+    M3 bit = transposed(inverse(xp.b));
+    V3 pn(pl_shape.p.x, pl_shape.p.y, pl_shape.p.z);
+    V3 point = xform(xp, pn * pl_shape.p.w);
+    Pl p;
+    p.n = normalized(xform(bit, pn));
+    p.d = dot(p.n, point);
+    V3 sup[MAX_SUPPORTS];
+    int n = 0, type = FEATURE_POINT;
+    get_supports(b, normalized(xform_inv(xb.b, -p.n)), sup, n, type);
+    bool found = false;
+    for (int i = 0; i < n; i++) {
+        V3 s = xform(xb, sup[i]);
+        if (pl_distance(p, s) >= 0) continue;
+        found = true;
+        V3 sa = pl_project(p, s);
+        if (swap_result) manifold_add(*c.m, s, sa);
+        else manifold_add(*c.m, sa, s);
+    }
+    return found;
+}
+
+// BradotCollisionSolver3D::solve_static (…collision_solver_3d.cpp:362-435) + sat_calculate_penetration dispatch (…sat.cpp:2296-2421)
+__device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, const X3 &xb, Manifold &m, V3 *sep_axis) {
+    Collector c;
+    c.m = &m;
+    c.swap = false;
+    c.collided = false;
+    c.prev_axis = sep_axis;
+    c.normal = V3();
+    uint32_t ta = sa.type, tb = sb.type;
+    if (min(ta, tb) == SH_PLANE) {
+        if (ta == SH_PLANE && tb == SH_PLANE) return false;
+        if (ta > tb) return col_plane(sb, xb, sa, xa, c, true);
+        return col_plane(sa, xa, sb, xb, c, false);
+    }
+    const Sh *A = &sa, *B = &sb;
+    const X3 *XA = &xa, *XB = &xb;
+    if (ta > tb) {
+        A = &sb; B = &sa; XA = &xb; XB = &xa;
+        uint32_t t = ta; ta = tb; tb = t;
+        c.swap = true;
+    }
+    if (ta == SH_SPHERE) {
+        if (tb == SH_SPHERE) col_sphere_sphere(*A, *XA, *B, *XB, c);
+        else if (tb == SH_BOX) col_sphere_box(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CAPSULE) col_sphere_capsule(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CONVEX) col_sphere_convex(*A, *XA, *B, *XB, c);
+    } else if (ta == SH_BOX) {
+        if (tb == SH_BOX) col_box_box(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CAPSULE) col_box_capsule(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CONVEX) col_box_convex(*A, *XA, *B, *XB, c);
+    } else if (ta == SH_CAPSULE) {
+        if (tb == SH_CAPSULE) col_capsule_capsule(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CONVEX) col_capsule_convex(*A, *XA, *B, *XB, c);
+    } else if (ta == SH_CONVEX && tb == SH_CONVEX) {
+        col_convex_convex(*A, *XA, *B, *XB, c);
+    }
+    return c.collided;
+}

@@ -1,0 +1,246 @@
+"""Host-side mirror of the PhysicsServer3D calls the rigid-body step needs, over the C ABI.
+
+This is the Python face of ``libbradot_physics_cuda.so`` (include/bradot_physics_cuda.h) used by
+the tests and ``bench.py``.  Method names follow the reference's server
+(servers/physics_server_3d.h:263-814: space_create, space_set_param, *_shape_create,
+body_* state access, joint_make_pin / joint_make_hinge, step, get_process_info); bodies are created
+in bulk from the scene records because one RID call per body is host-bound at 1 M bodies
+(hard part 8).
+
+There is no CPU fallback: if the CUDA library is missing or no GPU is usable the constructor raises.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import scenes
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbradot_physics_cuda.so")
+
+FIELD_TRANSFORM, FIELD_LINEAR_VELOCITY, FIELD_ANGULAR_VELOCITY, FIELD_ACTIVE = 0, 1, 2, 3
+FIELD_MASS_PROPS, FIELD_ITEM_BOX, FIELD_APPLIED_FORCE, FIELD_STILL_TIME = 4, 5, 6, 7
+_FIELD_WIDTH = {0: 12, 1: 3, 2: 3, 3: 1, 4: 16, 5: 14, 6: 6, 7: 1}
+
+SPACE_PARAM_CONTACT_RECYCLE_RADIUS, SPACE_PARAM_CONTACT_MAX_SEPARATION = 0, 1
+SPACE_PARAM_CONTACT_MAX_ALLOWED_PENETRATION, SPACE_PARAM_CONTACT_DEFAULT_BIAS = 2, 3
+SPACE_PARAM_BODY_LINEAR_VELOCITY_SLEEP_THRESHOLD, SPACE_PARAM_BODY_ANGULAR_VELOCITY_SLEEP_THRESHOLD = 4, 5
+SPACE_PARAM_BODY_TIME_TO_SLEEP, SPACE_PARAM_SOLVER_ITERATIONS = 6, 7
+SPACE_GRAVITY_X, SPACE_GRAVITY_Y, SPACE_GRAVITY_Z, SPACE_LINEAR_DAMP, SPACE_ANGULAR_DAMP = 100, 101, 102, 103, 104
+
+INFO_ACTIVE_OBJECTS, INFO_COLLISION_PAIRS, INFO_ISLAND_COUNT = 0, 1, 2  # PhysicsServer3D::ProcessInfo
+
+EXPORTS = [
+    "bpc_create", "bpc_destroy", "bpc_last_error", "bpc_set_stream", "bpc_space_create", "bpc_space_set_param",
+    "bpc_shape_create", "bpc_shape_create_convex", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
+    "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
+    "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64",
+]
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in ("active_objects", "collision_pairs", "island_count", "contact_pairs",
+                                              "colors", "overflow", "steps", "kernel_launches")]
+
+
+class PhysicsError(RuntimeError):
+    pass
+
+
+def load_library(path=LIB_PATH):
+    """dlopen the CUDA backend; raises if it has not been built (no fallback exists)."""
+    if not os.path.exists(path):
+        raise PhysicsError("CUDA backend %s is missing: run `python -m bradot_b200.build` (there is no CPU fallback)" % path)
+    lib = ctypes.CDLL(path)
+    vp, ci, cf = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+    lib.bpc_create.restype = vp
+    lib.bpc_create.argtypes = [ci]
+    lib.bpc_destroy.restype = None
+    lib.bpc_destroy.argtypes = [vp]
+    lib.bpc_last_error.restype = ctypes.c_char_p
+    lib.bpc_last_error.argtypes = [vp]
+    lib.bpc_set_stream.argtypes = [vp, vp]
+    lib.bpc_space_create.argtypes = [vp]
+    lib.bpc_space_set_param.argtypes = [vp, ci, ci, cf]
+    lib.bpc_shape_create.argtypes = [vp, ci, vp]
+    lib.bpc_shape_create_convex.argtypes = [vp, vp, ci, vp, vp, ci, vp, ci, vp, ci]
+    lib.bpc_bodies_create.argtypes = [vp, vp, ci]
+    lib.bpc_bodies_write.argtypes = [vp, ci, ci, ci, vp]
+    lib.bpc_bodies_read.argtypes = [vp, ci, ci, ci, vp]
+    lib.bpc_body_count.argtypes = [vp]
+    lib.bpc_joints_create.argtypes = [vp, vp, ci]
+    lib.bpc_step.argtypes = [vp, cf]
+    lib.bpc_synchronize.argtypes = [vp]
+    lib.bpc_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
+    lib.bpc_pair_count.argtypes = [vp]
+    lib.bpc_pairs_read.argtypes = [vp, vp, vp, vp]
+    lib.bpc_pairs_write.argtypes = [vp, ci, vp, vp, vp]
+    lib.bpc_set_solve_order.argtypes = [vp, ci, vp]
+    lib.bpc_sort_u64.argtypes = [vp, vp, vp, ci]
+    for name in EXPORTS:
+        if name not in ("bpc_create", "bpc_destroy", "bpc_last_error"):
+            getattr(lib, name).restype = ci
+    return lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+class PhysicsServerCUDA:
+    """One context on one GPU ("BradotPhysicsCUDA")."""
+
+    def __init__(self, device=0, stream=None):
+        self.lib = load_library()
+        self.ctx = self.lib.bpc_create(device)
+        if not self.ctx:
+            raise PhysicsError("bpc_create(%d) failed: no usable CUDA device (there is no CPU fallback)" % device)
+        if stream:
+            self._check(self.lib.bpc_set_stream(self.ctx, ctypes.c_void_p(stream)))
+        self.mesh_source = None
+
+    # -- plumbing -----------------------------------------------------------------------------
+    def _check(self, rc):
+        if rc < 0:
+            raise PhysicsError(self.lib.bpc_last_error(self.ctx).decode())
+        return rc
+
+    def finish(self):
+        if getattr(self, "ctx", None):
+            self.lib.bpc_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.finish()
+        except Exception:
+            pass
+
+    # -- spaces -------------------------------------------------------------------------------
+    def space_create(self):
+        return self._check(self.lib.bpc_space_create(self.ctx))
+
+    def space_set_param(self, space, param, value):
+        self._check(self.lib.bpc_space_set_param(self.ctx, space, param, float(value)))
+
+    # -- shapes -------------------------------------------------------------------------------
+    def shape_create(self, type_, params):
+        p = np.zeros(4, np.float32)
+        p[:len(params)] = params
+        return self._check(self.lib.bpc_shape_create(self.ctx, int(type_), _ptr(p)))
+
+    def world_boundary_shape_create(self, normal, d):
+        return self.shape_create(scenes.SHAPE_PLANE, (normal[0], normal[1], normal[2], d))
+
+    def sphere_shape_create(self, radius):
+        return self.shape_create(scenes.SHAPE_SPHERE, (radius,))
+
+    def box_shape_create(self, half_extents):
+        return self.shape_create(scenes.SHAPE_BOX, tuple(half_extents))
+
+    def capsule_shape_create(self, radius, height):
+        return self.shape_create(scenes.SHAPE_CAPSULE, (radius, height))
+
+    def convex_polygon_shape_create(self, mesh):
+        """mesh: dict with verts (n,3) f4, planes (f,4) f4, faces (f,2) i4, index (k,) i4, edges (e,4) i4."""
+        v = np.ascontiguousarray(mesh["verts"], np.float32)
+        pl = np.ascontiguousarray(mesh["planes"], np.float32)
+        fa = np.ascontiguousarray(mesh["faces"], np.int32)
+        ix = np.ascontiguousarray(mesh["index"], np.int32)
+        ed = np.ascontiguousarray(mesh["edges"], np.int32)
+        return self._check(self.lib.bpc_shape_create_convex(self.ctx, _ptr(v), len(v), _ptr(pl), _ptr(fa), len(fa), _ptr(ix), len(ix),
+                                                            _ptr(ed), len(ed)))
+
+    # -- bodies -------------------------------------------------------------------------------
+    def bodies_create(self, records):
+        rec = np.ascontiguousarray(records, scenes.BODY_DT)
+        return self._check(self.lib.bpc_bodies_create(self.ctx, _ptr(rec), len(rec)))
+
+    def body_count(self):
+        return self._check(self.lib.bpc_body_count(self.ctx))
+
+    def bodies_read(self, field, first=0, n=None):
+        n = self.body_count() - first if n is None else n
+        out = np.zeros((n, _FIELD_WIDTH[field]), np.float32)
+        self._check(self.lib.bpc_bodies_read(self.ctx, field, first, n, _ptr(out)))
+        return out
+
+    def bodies_write(self, field, values, first=0):
+        v = np.ascontiguousarray(values, np.float32).reshape(-1, _FIELD_WIDTH[field])
+        self._check(self.lib.bpc_bodies_write(self.ctx, field, first, len(v), _ptr(v)))
+
+    def joints_create(self, records):
+        rec = np.ascontiguousarray(records, scenes.JOINT_DT)
+        return self._check(self.lib.bpc_joints_create(self.ctx, _ptr(rec), len(rec)))
+
+    # -- stepping -----------------------------------------------------------------------------
+    def step(self, dt):
+        self._check(self.lib.bpc_step(self.ctx, float(dt)))
+
+    def sync(self):
+        self._check(self.lib.bpc_synchronize(self.ctx))
+
+    def stats(self):
+        s = Stats()
+        self._check(self.lib.bpc_get_stats(self.ctx, ctypes.byref(s)))
+        return {n: getattr(s, n) for n, _ in Stats._fields_}
+
+    def get_process_info(self, info):
+        s = self.stats()
+        return [s["active_objects"], s["collision_pairs"], s["island_count"]][info]
+
+    # -- pair / manifold snapshot ---------------------------------------------------------------
+    def pairs_read(self):
+        n = self._check(self.lib.bpc_pair_count(self.ctx))
+        ids = np.zeros((n, 4), np.int32)
+        pf = np.zeros((n, 3), np.float32)
+        cf = np.zeros((n, 4, 16), np.float32)
+        if n:
+            self._check(self.lib.bpc_pairs_read(self.ctx, _ptr(ids), _ptr(pf), _ptr(cf)))
+        return ids, pf, cf
+
+    def pairs_write(self, ids, pf, cf):
+        ids = np.ascontiguousarray(ids, np.int32).reshape(-1, 4)
+        pf = np.ascontiguousarray(pf, np.float32).reshape(-1, 3)
+        cf = np.ascontiguousarray(cf, np.float32).reshape(-1, 4, 16)
+        self._check(self.lib.bpc_pairs_write(self.ctx, len(ids), _ptr(ids), _ptr(pf), _ptr(cf)))
+
+    def set_solve_order(self, order):
+        o = np.ascontiguousarray(order, np.int32).reshape(-1, 3)
+        self._check(self.lib.bpc_set_solve_order(self.ctx, len(o), _ptr(o)))
+
+    def sort_u64(self, keys):
+        k = np.ascontiguousarray(keys, np.uint64)
+        out = np.zeros_like(k)
+        self._check(self.lib.bpc_sort_u64(self.ctx, _ptr(k), _ptr(out), len(k)))
+        return out
+
+    # -- scene loading --------------------------------------------------------------------------
+    def load_scene(self, sc, meshes=None):
+        """Build every space / shape / body / joint of a scenes.Scene.  ``meshes`` maps a convex
+        shape index to its hull (Geometry3D::MeshData layout), e.g. from an oracle dump."""
+        for _ in range(sc.n_spaces):
+            sp = self.space_create()
+            self.space_set_param(sp, SPACE_PARAM_SOLVER_ITERATIONS, sc.iterations)
+        for i, s in enumerate(sc.shapes):
+            if s["type"] == scenes.SHAPE_CONVEX:
+                if meshes is None or i not in meshes:
+                    raise PhysicsError("convex shape %d needs its hull mesh (the engine side runs ConvexHullComputer)" % i)
+                self.convex_polygon_shape_create(meshes[i])
+            else:
+                self.shape_create(int(s["type"]), s["p"])
+        first = self.bodies_create(sc.bodies) if len(sc.bodies) else 0
+        if len(sc.joints):
+            self.joints_create(sc.joints)
+        return first
+
+
+def meshes_from_dump(dump):
+    """Collect the convex hulls an oracle dump holds (oracle/ref_harness.cpp dump_meshes)."""
+    out = {}
+    for (name, idx), arr in dump.items():
+        if name == "mesh_verts":
+            out[idx] = {"verts": arr, "planes": dump[("mesh_planes", idx)], "faces": dump[("mesh_faces", idx)],
+                        "index": dump[("mesh_index", idx)], "edges": dump[("mesh_edges", idx)]}
+    return out

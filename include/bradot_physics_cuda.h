@@ -1,0 +1,132 @@
+/* bradot_physics_cuda.h -- C ABI of the B200 rigid-body step ("BradotPhysicsCUDA").
+ *
+ * This is the boundary the engine-side PhysicsServer3D backend binds: plain C
+ * structs, caller-owned host buffers, int return codes (0 = ok, <0 = error, text from
+ * bpc_last_error).  No exceptions and no C++/torch types cross it.  One context per GPU; calls on
+ * a context must be externally serialised (the engine has a single physics thread).
+ *
+ * Citations are relative to the reference tree; P3D = modules/bradot_physics_3d.
+ * Numeric values of shape types, body modes and body parameters are those of the reference enums
+ * (servers/physics_server_3d.h:247-259, 387-392, 439-451).
+ */
+#ifndef BRADOT_PHYSICS_CUDA_H
+#define BRADOT_PHYSICS_CUDA_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bpc_context bpc_context;
+
+enum { BPC_SHAPE_WORLD_BOUNDARY = 0, BPC_SHAPE_SPHERE = 2, BPC_SHAPE_BOX = 3, BPC_SHAPE_CAPSULE = 4, BPC_SHAPE_CONVEX_POLYGON = 6 };
+enum { BPC_BODY_MODE_STATIC = 0, BPC_BODY_MODE_KINEMATIC = 1, BPC_BODY_MODE_RIGID = 2, BPC_BODY_MODE_RIGID_LINEAR = 3 };
+enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1 };
+
+/* Bulk body description; one record per body.  Same layout as the record of the neutral scene
+ * file (bradot_b200/scenes.py BODY_DT).  Replaces the per-body call sequence body_create /
+ * body_set_mode / body_add_shape / body_set_param / body_set_state / body_set_space
+ * (P3D/bradot_physics_server_3d.cpp:438-760). */
+typedef struct bpc_body_desc {
+    uint32_t space, mode, shape, flags; /* flags: bit0 can_sleep, bit1 continuous cd (ignored), bit2 start asleep */
+    float xf[12];                       /* basis rows (9) then origin (3) */
+    float shape_xf[12];                 /* local transform of the single shape */
+    float linvel[3], angvel[3];
+    float mass, friction, bounce, gravity_scale, lin_damp, ang_damp;
+    uint32_t layer, mask;
+} bpc_body_desc;
+
+typedef struct bpc_joint_desc {
+    uint32_t type, body_a, body_b, flags; /* flags bit0: bodies do not collide with each other */
+    float frame_a[12], frame_b[12];       /* pin: origins only (local anchors); hinge: local frames */
+} bpc_joint_desc;
+
+/* PhysicsServer3D::SpaceParameter (servers/physics_server_3d.h:283-292) plus the default-area
+ * values a space carries (P3D/bradot_area_3d.h:50-55). */
+enum {
+    BPC_SPACE_CONTACT_RECYCLE_RADIUS = 0, BPC_SPACE_CONTACT_MAX_SEPARATION = 1, BPC_SPACE_CONTACT_MAX_ALLOWED_PENETRATION = 2,
+    BPC_SPACE_CONTACT_DEFAULT_BIAS = 3, BPC_SPACE_BODY_LINEAR_VELOCITY_SLEEP_THRESHOLD = 4,
+    BPC_SPACE_BODY_ANGULAR_VELOCITY_SLEEP_THRESHOLD = 5, BPC_SPACE_BODY_TIME_TO_SLEEP = 6, BPC_SPACE_SOLVER_ITERATIONS = 7,
+    BPC_SPACE_GRAVITY_X = 100, BPC_SPACE_GRAVITY_Y = 101, BPC_SPACE_GRAVITY_Z = 102, BPC_SPACE_LINEAR_DAMP = 103, BPC_SPACE_ANGULAR_DAMP = 104
+};
+
+/* Per-body state arrays for bulk read/write; `n` consecutive bodies starting at `first`. */
+enum {
+    BPC_FIELD_TRANSFORM = 0,        /* 12 floats: basis rows + origin          (body_get/set_state BODY_STATE_TRANSFORM) */
+    BPC_FIELD_LINEAR_VELOCITY = 1,  /* 3 floats                                (BODY_STATE_LINEAR_VELOCITY) */
+    BPC_FIELD_ANGULAR_VELOCITY = 2, /* 3 floats                                (BODY_STATE_ANGULAR_VELOCITY) */
+    BPC_FIELD_ACTIVE = 3,           /* 1 float (0/1)                           (BODY_STATE_SLEEPING, inverted) */
+    BPC_FIELD_MASS_PROPS = 4,       /* 16 floats: inv_mass, inv_inertia(3), com_local(3), principal axes rows(9) */
+    BPC_FIELD_ITEM_BOX = 5,         /* 14 floats: aabb_cache pos(3) size(3), stored min(3) max(3), num_pairs, id */
+    BPC_FIELD_APPLIED_FORCE = 6,    /* 6 floats: force, torque accumulated for the next step (body_apply_force/torque) */
+    BPC_FIELD_STILL_TIME = 7        /* 1 float */
+};
+
+typedef struct bpc_stats {
+    int32_t active_objects;  /* INFO_ACTIVE_OBJECTS   (P3D/bradot_physics_server_3d.cpp:1712-1726) */
+    int32_t collision_pairs; /* INFO_COLLISION_PAIRS */
+    int32_t island_count;    /* INFO_ISLAND_COUNT */
+    int32_t contact_pairs;   /* pairs whose narrowphase reported a collision this step */
+    int32_t colors;          /* sweep groups used by the solver this step */
+    int32_t overflow;        /* constraints that did not fit the colour budget (solved serially) */
+    int32_t steps;
+    int32_t kernel_launches; /* kernels launched by the last bpc_step */
+} bpc_stats;
+
+/* ---- lifecycle: BradotPhysicsServer3D::init / finish (P3D/bradot_physics_server_3d.cpp:1628-1630, 1704-1706) */
+bpc_context *bpc_create(int device);
+void bpc_destroy(bpc_context *ctx);
+const char *bpc_last_error(bpc_context *ctx);
+/* CUDA stream all work is enqueued on (cudaStream_t as void*); 0 = default stream. */
+int bpc_set_stream(bpc_context *ctx, void *cuda_stream);
+
+/* ---- spaces: space_create / space_set_param (P3D/bradot_physics_server_3d.cpp:144-191) */
+int bpc_space_create(bpc_context *ctx);
+int bpc_space_set_param(bpc_context *ctx, int space, int param, float value);
+
+/* ---- shapes: shape_create + shape_set_data (P3D/bradot_physics_server_3d.cpp:50-142; P3D/bradot_shape_3d.cpp _setup) */
+int bpc_shape_create(bpc_context *ctx, int type, const float params[4]);
+/* Convex hull in the layout of Geometry3D::MeshData (core/math/geometry_3d.h): the engine-side
+ * module runs ConvexHullComputer (host, set-up time only, P3D/bradot_shape_3d.cpp:1099) and hands
+ * the result over.  faces: per face (first index, index count) into `indices`; edges: per edge
+ * (vertex_a, vertex_b, face_a, face_b); planes: per face (nx, ny, nz, d). */
+int bpc_shape_create_convex(bpc_context *ctx, const float *verts, int n_verts, const float *planes, const int32_t *faces, int n_faces,
+                            const int32_t *indices, int n_indices, const int32_t *edges, int n_edges);
+
+/* ---- bodies */
+int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, int n); /* returns first body index */
+int bpc_bodies_write(bpc_context *ctx, int field, int first, int n, const float *host);
+int bpc_bodies_read(bpc_context *ctx, int field, int first, int n, float *host);
+int bpc_body_count(bpc_context *ctx);
+
+/* ---- joints: joint_make_pin / joint_make_hinge / joint_disable_collisions_between_bodies
+ * (P3D/bradot_physics_server_3d.cpp:1224-1246, 1388-1406) */
+int bpc_joints_create(bpc_context *ctx, const bpc_joint_desc *descs, int n);
+
+/* ---- the step: BradotPhysicsServer3D::step -> BradotStep3D::step for every space at once
+ * (P3D/bradot_physics_server_3d.cpp:1632-1648, P3D/bradot_step_3d.cpp:186-410) */
+int bpc_step(bpc_context *ctx, float dt);
+int bpc_synchronize(bpc_context *ctx);
+int bpc_get_stats(bpc_context *ctx, bpc_stats *out);
+
+/* ---- state snapshot of the pair/manifold cache (debug dumps, differential tests, checkpoint/restore).
+ * Pair record: body_a, body_b, contact_count, flags(bit0 collided, bit1 collide_A, bit2 collide_B).
+ * Pair floats: sep_axis(3).  Contact floats (4 per pair, 16 each):
+ *   local_A(3) local_B(3) normal(3) acc_normal acc_tangent(3) acc_bias acc_bias_com used          */
+int bpc_pair_count(bpc_context *ctx);
+int bpc_pairs_read(bpc_context *ctx, int32_t *pair_ids, float *pair_f, float *contacts);
+int bpc_pairs_write(bpc_context *ctx, int n_pairs, const int32_t *pair_ids, const float *pair_f, const float *contacts);
+/* Teacher-forced sweep order for differential tests: constraints are solved in exactly this
+ * sequence (sequential Gauss-Seidel semantics, P3D/bradot_step_3d.cpp:134-160) instead of the
+ * colouring.  order: n records (kind, a, b): kind 0 = body pair (a, b), kind 1 = joint index a.
+ * n = 0 returns to the default scheduling. */
+int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order);
+
+/* ---- utilities exposed for tests and tools */
+/* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */
+int bpc_sort_u64(bpc_context *ctx, const uint64_t *keys_in, uint64_t *keys_out, int n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
