@@ -96,6 +96,9 @@ struct SpaceParams {
     int iterations = 16;
 };
 
+// stages timed by bpc_set_profiling: forces, broadphase, islands, narrowphase, schedule, solve, integrate+sleep
+#define BPC_N_STAGES 7
+
 struct JointRec {
     uint32_t type, a, b, flags;
     float fa[12], fb[12];
@@ -122,6 +125,11 @@ struct bpc_context {
     bool shapes_dirty = true, joints_dirty = true, spaces_dirty = true;
     uint32_t *h_counters = nullptr; // pinned mirror of the device counters of the last step
     uint32_t launches = 0;          // kernels launched by the current / last step
+    // optional per-stage device timing (CUDA events on the step's stream)
+    bool profiling = false, ev_pending = false;
+    cudaEvent_t ev[BPC_N_STAGES + 1] = {};
+    double stage_ms[BPC_N_STAGES] = {};
+    uint32_t stage_steps = 0;
     DevBuf<JointRec> d_joints;
     DevBuf<uint64_t> forced_keys;
 
@@ -199,7 +207,7 @@ struct bpc_context {
 };
 
 enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIVE = 4, CNT_ISLANDS = 5, CNT_CONTACTS = 6,
-       CNT_OVERFLOW = 7, CNT_ROUND = 8, CNT_N = 16 };
+       CNT_OVERFLOW = 7, CNT_ROUND = 8, CNT_ACTIVE_CONTACTS = 10, CNT_N = 16 };
 
 #define BPC_CHECK(x)                                                                                  \
     do {                                                                                              \

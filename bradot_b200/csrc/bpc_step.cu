@@ -62,6 +62,41 @@ static int forced_schedule(bpc_context *ctx) {
     return 0;
 }
 
+// fold the event pairs of the previous profiled step into the per-stage totals
+static int collect_stage_times(bpc_context *ctx) {
+    if (!ctx->ev_pending) return 0;
+    BPC_CHECK(cudaEventSynchronize(ctx->ev[BPC_N_STAGES]));
+    for (int i = 0; i < BPC_N_STAGES; i++) {
+        float ms = 0.f;
+        BPC_CHECK(cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]));
+        ctx->stage_ms[i] += ms;
+    }
+    ctx->stage_steps++;
+    ctx->ev_pending = false;
+    return 0;
+}
+
+extern "C" int bpc_set_profiling(bpc_context *ctx, int on) {
+    if (!ctx) return -1;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (on && !ctx->ev[0]) {
+        for (int i = 0; i <= BPC_N_STAGES; i++) BPC_CHECK(cudaEventCreate(&ctx->ev[i]));
+    }
+    if (collect_stage_times(ctx)) return -1;
+    ctx->profiling = on != 0;
+    for (int i = 0; i < BPC_N_STAGES; i++) ctx->stage_ms[i] = 0.0;
+    ctx->stage_steps = 0;
+    return 0;
+}
+
+extern "C" int bpc_get_stage_times(bpc_context *ctx, double *ms_out, int *steps_out) {
+    if (!ctx || !ms_out) return -1;
+    if (collect_stage_times(ctx)) return -1;
+    for (int i = 0; i < BPC_N_STAGES; i++) ms_out[i] = ctx->stage_ms[i];
+    if (steps_out) *steps_out = (int)ctx->stage_steps;
+    return 0;
+}
+
 extern "C" int bpc_step(bpc_context *ctx, float dt) {
     if (!ctx) return -1;
     if (!(dt > 0.f)) return fail(ctx, "bpc_step: dt must be positive");
@@ -71,23 +106,35 @@ extern "C" int bpc_step(bpc_context *ctx, float dt) {
     cudaStream_t st = ctx->stream;
     ctx->launches = 0;
     BPC_CHECK(cudaMemsetAsync(ctx->counters.p, 0, CNT_N * sizeof(uint32_t), st));
+    if (ctx->profiling && collect_stage_times(ctx)) return -1;
+#define STAGE(i)                                                   \
+    if (ctx->profiling) BPC_CHECK(cudaEventRecord(ctx->ev[i], st))
+    STAGE(0);
     if (bpc_launch_integrate_forces(ctx, dt)) return -1;
+    STAGE(1);
     if (bpc_launch_broadphase(ctx)) return -1;
+    STAGE(2);
     if (bpc_launch_islands(ctx)) return -1;
+    STAGE(3);
     if (bpc_launch_narrowphase(ctx)) return -1;
     uint32_t np = ctx->n_pairs[ctx->cur];
     if (np) {
         k_count_collided<<<nblk(np, 128), 128, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->counters.p);
         ctx->launches += 1;
     }
+    STAGE(4);
     if (ctx->n_forced_levels) {
         if (forced_schedule(ctx)) return -1;
     } else {
         if (bpc_launch_schedule(ctx)) return -1;
     }
+    STAGE(5);
     if (bpc_launch_solver(ctx, dt)) return -1;
+    STAGE(6);
     if (bpc_launch_integrate_velocities(ctx, dt)) return -1;
     if (bpc_launch_sleep(ctx, dt)) return -1;
+    STAGE(7);
+    if (ctx->profiling) ctx->ev_pending = true;
     BPC_CHECK(cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     ctx->step_count++;
     ctx->last_dt = dt;
@@ -103,6 +150,7 @@ extern "C" int bpc_get_stats(bpc_context *ctx, bpc_stats *out) {
     out->contact_pairs = (int)ctx->h_counters[CNT_CONTACTS];
     out->colors = ctx->n_forced_levels ? (int)ctx->n_forced_levels : (int)ctx->h_counters[CNT_COLORS];
     out->overflow = (int)ctx->h_counters[CNT_OVERFLOW];
+    out->active_contacts = (int)ctx->h_counters[CNT_ACTIVE_CONTACTS];
     out->steps = (int)ctx->step_count;
     out->kernel_launches = (int)ctx->launches;
     return 0;

@@ -345,6 +345,7 @@ int bpc_build_tree(bpc_context *ctx) {
     while ((1u << sbits) < nsp) sbits++;
     uint64_t mask = (1ull << (30 + sbits)) - 1ull;
     if (bpc_radix_sort(ctx, &ctx->keys.p, &ctx->keys_alt.p, &ctx->vals.p, &ctx->vals_alt.p, n, mask)) return -1;
+    ctx->launches += 4 + (n >= 2 ? 2 : 0);
     k_leaves<<<nblk(n, BP_THREADS), BP_THREADS, 0, st>>>(n, ctx->vals.p, ctx->items.p, ctx->meta.p, ctx->leaf_min.p, ctx->leaf_max.p);
     if (n >= 2) {
         BPC_CHECK(cudaMemsetAsync(ctx->node_flag.p, 0, (size_t)n * sizeof(uint32_t), st));
@@ -369,6 +370,7 @@ int bpc_launch_broadphase(bpc_context *ctx) {
             k_traverse<<<nblk(n, BP_THREADS), BP_THREADS, 0, st>>>((int)n, ctx->leaf_min.p, ctx->leaf_max.p, ctx->nodes.p, ctx->meta.p,
                                                                    ctx->items.p, ctx->big_items.p, ctx->n_big, ctx->pair_keys_raw.p,
                                                                    (uint32_t)ctx->pair_cap, ctx->counters.p + CNT_PAIRS);
+            ctx->launches += 1;
         }
         BPC_CHECK(cudaMemcpyAsync(&found, ctx->counters.p + CNT_PAIRS, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
         BPC_CHECK(cudaStreamSynchronize(st));
@@ -392,6 +394,7 @@ int bpc_launch_broadphase(bpc_context *ctx) {
         k_match<<<nblk(found, BP_THREADS), BP_THREADS, 0, st>>>(found, kdst, ctx->n_pairs[ctx->cur], ctx->pair_keys[ctx->cur].p,
                                                                 ctx->pair_hdr[ctx->cur].p, ctx->cgeo[ctx->cur].p, ctx->cacc[ctx->cur].p,
                                                                 ctx->pair_hdr[nxt].p, ctx->cgeo[nxt].p, ctx->cacc[nxt].p, ctx->npairs.p);
+        ctx->launches += 1;
     }
     BPC_CHECK(cudaGetLastError());
     ctx->n_pairs[nxt] = found;

@@ -103,6 +103,7 @@ int bpc_launch_islands(bpc_context *ctx) {
     k_cc_flatten<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->meta.p, ctx->island_flag.p);
     if (np) k_island_mark<<<nblk(np, GR_THREADS), GR_THREADS, 0, st>>>(np, ctx->pair_keys[ctx->cur].p, ctx->meta.p, ctx->island.p,
                                                                         ctx->island_flag.p, ctx->counters.p);
+    ctx->launches += 2 + (np ? 2 : 0) + (nj ? 1 : 0);
     BPC_CHECK(cudaGetLastError());
     return 0;
 }
@@ -283,6 +284,7 @@ int bpc_launch_schedule(bpc_context *ctx) {
     k_color_hist<<<hb, GR_THREADS, 0, st>>>(ctx->con_color.p, nj, ctx->counters.p, start);
     k_color_scan<<<1, 32, 0, st>>>(start, cursor, ctx->counters.p);
     k_color_scatter<<<hb, GR_THREADS, 0, st>>>(ctx->con_color.p, ctx->con_list.p, nj, ctx->counters.p, cursor, ctx->con_sorted.p);
+    ctx->launches += 4 + (np ? 1 : 0);
     BPC_CHECK(cudaGetLastError());
     return 0;
 }

@@ -264,6 +264,7 @@ int bpc_launch_integrate_forces(bpc_context *ctx, float dt) {
     if (!n) return 0;
     k_integrate_forces<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->vel.p, ctx->props.p, ctx->forces.p, ctx->massw.p,
                                                                             ctx->meta.p, ctx->d_spaces.p, ctx->counters.p);
+    ctx->launches += 1;
     BPC_CHECK(cudaGetLastError());
     return 0;
 }
@@ -274,6 +275,7 @@ int bpc_launch_integrate_velocities(bpc_context *ctx, float dt) {
     k_integrate_velocities<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->xf.p, ctx->vel.p, ctx->massw.p, ctx->props.p,
                                                                                 ctx->meta.p, ctx->shape_xf.p, ctx->shape_id.p,
                                                                                 ctx->shapes.p, ctx->items.p, ctx->npairs.p);
+    ctx->launches += 1;
     BPC_CHECK(cudaGetLastError());
     return 0;
 }
@@ -299,6 +301,7 @@ int bpc_launch_sleep(bpc_context *ctx, float dt) {
     k_sleep_test<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->vel.p, ctx->props.p, ctx->meta.p, ctx->d_spaces.p,
                                                                       ctx->island.p, ctx->island_flag.p);
     k_sleep_apply<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, ctx->meta.p, ctx->island.p, ctx->island_flag.p);
+    ctx->launches += 2;
     BPC_CHECK(cudaGetLastError());
     return 0;
 }

@@ -156,6 +156,7 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
     a.n_except = ctx->n_except;
     a.counters = ctx->counters.p;
     k_pair_setup<<<(n + NP_THREADS - 1) / NP_THREADS, NP_THREADS, 0, ctx->stream>>>(a);
+    ctx->launches += 1;
     BPC_CHECK(cudaGetLastError());
     return 0;
 }

@@ -106,6 +106,7 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
         pvA = f4v(pa.prev_lin); pwA = f4v(pa.prev_ang); pvB = f4v(pb.prev_lin); pwB = f4v(pb.prev_ang);
     }
     bool any = false;
+    int n_active = 0;
     for (int c = 0; c < count; c++) {
         ContactGeo g = a.geo[(size_t)k * 4 + c];
         ContactAcc ac = a.acc[(size_t)k * 4 + c];
@@ -146,10 +147,12 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
         sc.b.w = 1.f;
         a.sc[(size_t)s * 4 + c] = sc;
         any = true;
+        n_active++;
     }
     if (any) {
         if (cA) store_body(a, ia, A);
         if (cB) store_body(a, ib, B);
+        atomicAdd(&a.counters[CNT_ACTIVE_CONTACTS], (uint32_t)n_active);
     }
     a.info[s] = make_uint4(ia, ib, (uint32_t)count | (cA ? 0x200u : 0u) | (cB ? 0x400u : 0u) | (any ? 0x800u : 0u), k);
 }
@@ -351,5 +354,6 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     dim3 grid(ctx->sm_count * per_sm), block(SV_THREADS);
     void *args[] = { &a };
     BPC_CHECK(cudaLaunchCooperativeKernel((void *)k_solve, grid, block, args, 0, st));
+    ctx->launches += 1;
     return 0;
 }

@@ -139,6 +139,7 @@ int bpc_radix_sort(bpc_context *ctx, uint64_t **keys, uint64_t **keys_alt, uint3
         } else {
             k_radix_scatter<false><<<nb, RS_THREADS, 0, ctx->stream>>>(*keys, *keys_alt, nullptr, nullptr, hist, totals, n, shift, nb);
         }
+        ctx->launches += 3;
         uint64_t *tk = *keys;
         *keys = *keys_alt;
         *keys_alt = tk;

@@ -35,13 +35,14 @@ EXPORTS = [
     "bpc_create", "bpc_destroy", "bpc_last_error", "bpc_set_stream", "bpc_space_create", "bpc_space_set_param",
     "bpc_shape_create", "bpc_shape_create_convex", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
     "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
-    "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64",
+    "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
 ]
+STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
 
 
 class Stats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in ("active_objects", "collision_pairs", "island_count", "contact_pairs",
-                                              "colors", "overflow", "steps", "kernel_launches")]
+                                              "colors", "overflow", "steps", "kernel_launches", "active_contacts")]
 
 
 class PhysicsError(RuntimeError):
@@ -78,6 +79,8 @@ def load_library(path=LIB_PATH):
     lib.bpc_pairs_write.argtypes = [vp, ci, vp, vp, vp]
     lib.bpc_set_solve_order.argtypes = [vp, ci, vp]
     lib.bpc_sort_u64.argtypes = [vp, vp, vp, ci]
+    lib.bpc_set_profiling.argtypes = [vp, ci]
+    lib.bpc_get_stage_times.argtypes = [vp, vp, vp]
     for name in EXPORTS:
         if name not in ("bpc_create", "bpc_destroy", "bpc_last_error"):
             getattr(lib, name).restype = ci
@@ -185,6 +188,16 @@ class PhysicsServerCUDA:
         s = Stats()
         self._check(self.lib.bpc_get_stats(self.ctx, ctypes.byref(s)))
         return {n: getattr(s, n) for n, _ in Stats._fields_}
+
+    def set_profiling(self, on):
+        self._check(self.lib.bpc_set_profiling(self.ctx, 1 if on else 0))
+
+    def stage_times(self):
+        """({stage: total ms}, steps) accumulated since set_profiling(True)."""
+        ms = np.zeros(len(STAGES), np.float64)
+        n = ctypes.c_int(0)
+        self._check(self.lib.bpc_get_stage_times(self.ctx, _ptr(ms), ctypes.byref(n)))
+        return dict(zip(STAGES, ms.tolist())), n.value
 
     def get_process_info(self, info):
         s = self.stats()

@@ -71,6 +71,7 @@ typedef struct bpc_stats {
     int32_t overflow;        /* constraints that did not fit the colour budget (solved serially) */
     int32_t steps;
     int32_t kernel_launches; /* kernels launched by the last bpc_step */
+    int32_t active_contacts; /* contacts with positive depth handed to the solver this step */
 } bpc_stats;
 
 /* ---- lifecycle: BradotPhysicsServer3D::init / finish (P3D/bradot_physics_server_3d.cpp:1628-1630, 1704-1706) */
@@ -108,6 +109,13 @@ int bpc_joints_create(bpc_context *ctx, const bpc_joint_desc *descs, int n);
 int bpc_step(bpc_context *ctx, float dt);
 int bpc_synchronize(bpc_context *ctx);
 int bpc_get_stats(bpc_context *ctx, bpc_stats *out);
+/* Per-stage device time, the counterpart of the reference's five ELAPSED_TIME_* phases
+ * (P3D/bradot_space_3d.h:66-74, P3D/bradot_step_3d.cpp:202-404): CUDA events on the step's stream.
+ * Stages: 0 integrate forces, 1 broadphase, 2 islands, 3 narrowphase (constraint setup),
+ * 4 sweep scheduling, 5 pre-solve + solve, 6 integrate velocities + sleep.  ms_out[7] are totals
+ * since profiling was switched on, over *steps_out steps. */
+int bpc_set_profiling(bpc_context *ctx, int on);
+int bpc_get_stage_times(bpc_context *ctx, double *ms_out, int *steps_out);
 
 /* ---- state snapshot of the pair/manifold cache (debug dumps, differential tests, checkpoint/restore).
  * Pair record: body_a, body_b, contact_count, flags(bit0 collided, bit1 collide_A, bit2 collide_B).
