@@ -5,6 +5,8 @@
 // Per pass: k_radix_hist (per-tile digit histogram, digit-major) -> k_radix_rowscan (one block per
 // digit scans its row of tile counts) -> k_radix_scatter (stable rank inside the tile with
 // warp match + per-warp counters).  HBM traffic per pass: keys read twice, written once.
+#include <cstdio>
+
 #include "bpc_internal.h"
 
 #define RS_THREADS 256
@@ -145,5 +147,83 @@ int bpc_radix_sort(bpc_context *ctx, uint64_t **keys, uint64_t **keys_alt, uint3
         *keys_alt = tk;
     }
     BPC_CHECK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// bpc_sort_u64_noalloc: the same three kernels, for callers that are not allowed to allocate.
+//
+// Who that is: code that hands us device buffers it obtained elsewhere and must not trigger a
+// cudaMalloc/cudaFree while it runs -- an engine plugin working inside a fixed device arena, a
+// render/physics thread with a "no driver allocation after start-up" rule (cudaMalloc can
+// synchronise the whole device and stall every stream), or a host that preallocated everything
+// before entering a latency-critical loop.  bpc_sort_u64 grows context-owned buffers on demand,
+// which such callers cannot tolerate, so this variant keeps ALL of its scratch (one ping-pong key
+// buffer plus the per-tile digit histograms) in a fixed array that is part of the loaded module.
+//
+// Cost and limits: every GPU that loads the library holds BPC_NOALLOC_SCRATCH_BYTES (about
+// 0.56 MB) until the process exits; at most BPC_NOALLOC_MAX_KEYS keys per call.  All calls share
+// the one array, so two calls whose kernels may overlap on the GPU (different streams, different
+// host threads) race on it -- serialise them.  The array keeps the previous call's contents, which
+// is harmless: every histogram cell and every scratch key a pass reads was written earlier in the
+// same call, so nothing has to start at zero and nothing is cleared.
+#define BPC_NOALLOC_MAX_KEYS 65536
+#define BPC_NOALLOC_MAX_TILES ((BPC_NOALLOC_MAX_KEYS + RS_TILE - 1) / RS_TILE)
+#define BPC_NOALLOC_KEY_BYTES ((size_t)BPC_NOALLOC_MAX_KEYS * sizeof(uint64_t))
+#define BPC_NOALLOC_HIST_WORDS ((size_t)256 * BPC_NOALLOC_MAX_TILES + 256)
+#define BPC_NOALLOC_SCRATCH_BYTES (BPC_NOALLOC_KEY_BYTES + BPC_NOALLOC_HIST_WORDS * sizeof(uint32_t))
+#define BPC_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[BPC_NOALLOC_SCRATCH_BYTES];
+// Device address of g_noalloc_scratch on each GPU.  In host code the symbol name itself is only a
+// host-side handle, never a device pointer: the address has to be asked for, per device.
+static unsigned char *g_noalloc_addr[BPC_NOALLOC_MAX_DEVICES] = {};
+static thread_local char g_noalloc_err[256] = "";
+
+extern "C" const char *bpc_noalloc_last_error(void) { return g_noalloc_err; }
+
+static int noalloc_fail(const char *what, cudaError_t e) {
+    if (e != cudaSuccess) snprintf(g_noalloc_err, sizeof(g_noalloc_err), "%s: %s", what, cudaGetErrorString(e));
+    else snprintf(g_noalloc_err, sizeof(g_noalloc_err), "%s", what);
+    return -1;
+}
+
+extern "C" int bpc_sort_u64_noalloc(const uint64_t *d_keys_in, uint64_t *d_keys_out, int n, void *cuda_stream) {
+    g_noalloc_err[0] = 0;
+    if (n < 0 || (n > 0 && (!d_keys_in || !d_keys_out))) return noalloc_fail("bpc_sort_u64_noalloc: bad arguments", cudaSuccess);
+    if (n > BPC_NOALLOC_MAX_KEYS) {
+        snprintf(g_noalloc_err, sizeof(g_noalloc_err), "bpc_sort_u64_noalloc: %d keys exceed the fixed scratch (at most %d per call)", n,
+                 BPC_NOALLOC_MAX_KEYS);
+        return -1;
+    }
+    if (n == 0) return 0;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return noalloc_fail("bpc_sort_u64_noalloc: cudaGetDevice", e);
+    if (dev < 0 || dev >= BPC_NOALLOC_MAX_DEVICES) return noalloc_fail("bpc_sort_u64_noalloc: device index out of range", cudaSuccess);
+    if (!g_noalloc_addr[dev]) {
+        // one-time set-up for this device, with this device current
+        unsigned char *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return noalloc_fail("bpc_sort_u64_noalloc: cudaGetSymbolAddress(scratch)", e);
+        g_noalloc_addr[dev] = p;
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    uint64_t *tmp = (uint64_t *)g_noalloc_addr[dev];
+    uint32_t *hist = (uint32_t *)(g_noalloc_addr[dev] + BPC_NOALLOC_KEY_BYTES);
+    uint32_t un = (uint32_t)n, nb = (un + RS_TILE - 1) / RS_TILE;
+    uint32_t *totals = hist + (size_t)256 * nb;
+    // eight passes: in -> tmp -> out -> tmp -> ... -> out; the caller's input is never written
+    const uint64_t *src = d_keys_in;
+    for (int pass = 0; pass < 8; pass++) {
+        uint64_t *dst = (pass & 1) ? d_keys_out : tmp;
+        int shift = pass * 8;
+        k_radix_hist<<<nb, RS_THREADS, 0, st>>>(src, hist, un, shift, nb);
+        k_radix_rowscan<<<256, RS_THREADS, 0, st>>>(hist, totals, nb);
+        k_radix_scatter<false><<<nb, RS_THREADS, 0, st>>>(src, dst, nullptr, nullptr, hist, totals, un, shift, nb);
+        src = dst;
+    }
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return noalloc_fail("bpc_sort_u64_noalloc: kernel launch", e);
     return 0;
 }

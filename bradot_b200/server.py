@@ -36,6 +36,7 @@ EXPORTS = [
     "bpc_shape_create", "bpc_shape_create_convex", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
     "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
+    "bpc_sort_u64_noalloc", "bpc_noalloc_last_error",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
 
@@ -79,10 +80,14 @@ def load_library(path=LIB_PATH):
     lib.bpc_pairs_write.argtypes = [vp, ci, vp, vp, vp]
     lib.bpc_set_solve_order.argtypes = [vp, ci, vp]
     lib.bpc_sort_u64.argtypes = [vp, vp, vp, ci]
+    lib.bpc_sort_u64_noalloc.argtypes = [vp, vp, ci, vp]
+    lib.bpc_sort_u64_noalloc.restype = ci
+    lib.bpc_noalloc_last_error.argtypes = []
+    lib.bpc_noalloc_last_error.restype = ctypes.c_char_p
     lib.bpc_set_profiling.argtypes = [vp, ci]
     lib.bpc_get_stage_times.argtypes = [vp, vp, vp]
     for name in EXPORTS:
-        if name not in ("bpc_create", "bpc_destroy", "bpc_last_error"):
+        if name not in ("bpc_create", "bpc_destroy", "bpc_last_error", "bpc_noalloc_last_error"):
             getattr(lib, name).restype = ci
     return lib
 

@@ -134,6 +134,27 @@ int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order);
 /* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */
 int bpc_sort_u64(bpc_context *ctx, const uint64_t *keys_in, uint64_t *keys_out, int n);
 
+/* Allocation-free variant of the key sort.  It has no counterpart in the reference; it exists for
+ * hosts that hand over device buffers of their own and may not cause a cudaMalloc / cudaFree while
+ * they run (a plugin confined to a fixed device arena, a frame or physics loop with a "no driver
+ * allocation after start-up" rule, anything that preallocates and then must stay free of the
+ * device-wide stalls an allocation can bring).  It needs no context and allocates nothing, on the
+ * device or through any library: its scratch is a fixed array inside the loaded module, about
+ * 0.56 MB that every GPU using the library holds until the process ends.
+ *   d_keys_in / d_keys_out : DEVICE pointers to n keys each (caller-owned, may not alias)
+ *   n                      : at most BPC_SORT_NOALLOC_MAX_KEYS; larger sizes are rejected with an error
+ *   cuda_stream            : cudaStream_t the kernels are enqueued on; the result is ready once that
+ *                            stream has reached this point (the call itself does not wait)
+ * The first call on each device also looks up where the scratch lives on that device; that lookup
+ * is not a stream operation, so make the first call before starting any stream capture.
+ * All calls share the one scratch array: calls that may overlap on the GPU (other streams, other
+ * threads) race on it and must be serialised by the caller.  The array keeps what the previous call
+ * left in it; no part of it has to be cleared, because each pass writes every cell it later reads.
+ * Returns 0, or -1 with the reason available from bpc_noalloc_last_error() (per host thread). */
+#define BPC_SORT_NOALLOC_MAX_KEYS 65536
+int bpc_sort_u64_noalloc(const uint64_t *d_keys_in, uint64_t *d_keys_out, int n, void *cuda_stream);
+const char *bpc_noalloc_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif
