@@ -33,7 +33,11 @@ METRIC = "rigid_body_steps_per_s"
 UNIT = "body-steps/s"
 
 
-def build_scene(name, scale):
+def build_scene(name, scale, rank=0, world=1):
+    if name == "c5":
+        total = max(world, int(round(4096 * scale)))
+        lo, hi = shard_range(total, rank, world)
+        return scenes.batched_worlds(hi - lo, seed0=1000 + lo), "C5: %d independent spaces x 256 mixed bodies, sharded by space" % total
     if name == "c2":
         if scale >= 1.0:
             return scenes.spheres_container(50, 40, 50), "C2: 100k spheres r=0.25 on a 50x40x50 lattice falling into 5 static planes"
@@ -45,6 +49,32 @@ def build_scene(name, scale):
         n = max(3, int(round(100 * scale ** (1 / 3.0))))
         return scenes.mixed_pile(n), "C3: %d mixed box/sphere/capsule bodies" % n ** 3
     raise SystemExit("unknown scene " + name)
+
+
+def shard_range(n_units, rank, world):
+    """Contiguous block of independent units (spaces) owned by `rank`; sizes differ by at most one."""
+    base, rem = divmod(n_units, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def reduce_max_ms(ms, device="cuda"):
+    """max over ranks of a duration (the job is as slow as its slowest rank)."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([ms], dtype=torch.float64, device=device)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def reduce_sum(x, device="cuda"):
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
 
 
 def n_dynamic(sc):
@@ -137,8 +167,9 @@ def cuda_arm(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    sc, label = build_scene(args.scene, args.scale)
+    sc, label = build_scene(args.scene, args.scale, rank, world)
     nd = n_dynamic(sc)
+    total_nd = reduce_sum(float(nd))
     stream = torch.cuda.current_stream().cuda_stream
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")  # 256 MiB > 126 MB L2
 
@@ -174,11 +205,8 @@ def cuda_arm(args):
     ps.set_profiling(False)
     sampler.stop_flag = True
     sampler.join()
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = nd * args.steps * world / (ms_max * 1e-3)
+    ms_max = reduce_max_ms(ms)
+    value = total_nd * args.steps / (ms_max * 1e-3)
     ps.finish()
 
     # ---------------- end-to-end arm: host buffers through the C ABI, fresh context, same schedule
@@ -202,10 +230,7 @@ def cuda_arm(args):
     e1.record()
     barrier()
     e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)
-    t2 = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-    e2e_value = nd * args.steps * world / (float(t2.item()) * 1e-3)
+    e2e_value = total_nd * args.steps / (reduce_max_ms(e2e_ms) * 1e-3)
     ps2.finish()
 
     if rank == 0:
@@ -222,8 +247,9 @@ def cuda_arm(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_max / k, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": label, "bodies": nd, "dt": float(sc.dt), "solver_iterations": iters,
-                       "parallelism": "replicas only (%d independent copies)" % world if world > 1 else "1 GPU",
+            "config": {"workload": label, "bodies": int(total_nd), "dt": float(sc.dt), "solver_iterations": iters,
+                       "parallelism": ("spaces sharded over %d ranks, no data-path collective" % world if args.scene == "c5" else
+                                       "replicas only (%d independent copies)" % world) if world > 1 else "1 GPU",
                        "l2": "256 MiB buffer written between timed steps (L2 flush)",
                        "avg_broadphase_pairs": acc["collision_pairs"] / k, "avg_contact_pairs": pc, "avg_contacts_per_pair": cbar,
                        "avg_colors": acc["colors"] / k},

@@ -2,7 +2,7 @@
 //
 // Every function mirrors the ARITHMETIC ORDER of the reference's value types so that
 // structural decisions (AABB compares, SAT axis choice, feature thresholds) agree bit
-// for bit with the CPU oracle.  The library is compiled with -fmad=false (the reference
+// for bit with the CPU reference.  The library is compiled with -fmad=false (the reference
 // is built with -ffp-contract=off, platform/linuxbsd/detect.py:177).
 //   core/math/vector3.h:198-209,477-503   cross / dot / length / normalize
 //   core/math/basis.h:114-122,252-257,307-319  tdot / operator* / xform / xform_inv
