@@ -77,19 +77,14 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_flatten(uint32_t n, uint32_t 
 }
 
 // island_count statistic: islands with at least one constraint (bradot_step_3d.cpp:292-294, 337)
-__global__ void __launch_bounds__(GR_THREADS) k_island_mark(uint32_t n_pairs, const uint64_t *__restrict__ keys, const uint4 *__restrict__ meta,
-                                                            const uint32_t *__restrict__ label, uint32_t *__restrict__ flag,
-                                                            uint32_t *__restrict__ counters) {
-    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n_pairs) return;
-    uint64_t key = keys[k];
-    uint32_t a = (uint32_t)(key >> 32), b = (uint32_t)key;
-    uint32_t r = label[(meta[a].x & 0xffu) != MODE_STATIC ? a : b];
-    uint32_t f = flag[r];
-    if ((f & 1u) && !(f & 4u)) {
-        uint32_t old = atomicOr(&flag[r], 4u);
-        if (!(old & 4u)) atomicAdd(&counters[CNT_ISLANDS], 1u);
-    }
+// A component of two or more bodies gives every member an edge, and a lone body's pairs all involve
+// it, so "island has a constraint" == "its root body has at least one pair".
+__global__ void __launch_bounds__(GR_THREADS) k_island_count(uint32_t n, const uint32_t *__restrict__ label, const uint32_t *__restrict__ flag,
+                                                             const uint32_t *__restrict__ npairs, uint32_t *__restrict__ counters) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool isl = i < n && label[i] == i && (flag[i] & 1u) && npairs[i] > 0;
+    uint32_t m = __ballot_sync(0xffffffffu, isl);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(&counters[CNT_ISLANDS], __popc(m));
 }
 
 int bpc_launch_islands(bpc_context *ctx) {
@@ -101,9 +96,8 @@ int bpc_launch_islands(bpc_context *ctx) {
     uint32_t nj = (uint32_t)ctx->h_joints.size();
     if (nj) k_cc_union_joints<<<nblk(nj, GR_THREADS), GR_THREADS, 0, st>>>(nj, ctx->d_joints.p, ctx->meta.p, ctx->island.p);
     k_cc_flatten<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->meta.p, ctx->island_flag.p);
-    if (np) k_island_mark<<<nblk(np, GR_THREADS), GR_THREADS, 0, st>>>(np, ctx->pair_keys[ctx->cur].p, ctx->meta.p, ctx->island.p,
-                                                                        ctx->island_flag.p, ctx->counters.p);
-    ctx->launches += 2 + (np ? 2 : 0) + (nj ? 1 : 0);
+    k_island_count<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->island_flag.p, ctx->npairs.p, ctx->counters.p);
+    ctx->launches += 3 + (np ? 1 : 0) + (nj ? 1 : 0);
     BPC_CHECK(cudaGetLastError());
     return 0;
 }
@@ -111,11 +105,18 @@ int bpc_launch_islands(bpc_context *ctx) {
 // ---------------------------------------------------------------------------------------------
 // Constraint list: colliding pairs (collided bit set by the narrowphase), then joints.
 // Constraint id: pair index k, or n_pairs + joint index.
-__global__ void __launch_bounds__(GR_THREADS) k_con_collect(uint32_t n_pairs, const PairHdr *__restrict__ hdr, uint32_t *__restrict__ list,
+__global__ void __launch_bounds__(GR_THREADS) k_con_collect(uint32_t n_pairs, const PairHdr *__restrict__ hdr, const uint64_t *__restrict__ keys,
+                                                            const uint4 *__restrict__ meta, const uint32_t *__restrict__ island,
+                                                            const uint32_t *__restrict__ island_flag, uint32_t *__restrict__ list,
                                                             uint32_t *__restrict__ counters) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     bool take = false;
-    if (k < n_pairs) take = (__float_as_uint(hdr[k].sep.w) & 0x100u) != 0;
+    if (k < n_pairs && (__float_as_uint(hdr[k].sep.w) & 0x100u) != 0) {
+        // pairs of sleeping islands keep last step's flags: they are not constraints of this step
+        uint64_t key = keys[k];
+        uint32_t a = (uint32_t)(key >> 32), b = (uint32_t)key;
+        take = (island_flag[island[(meta[a].x & 0xffu) != MODE_STATIC ? a : b]] & 1u) != 0;
+    }
     uint32_t m = __ballot_sync(0xffffffffu, take);
     if (!m) return;
     uint32_t lane = threadIdx.x & 31, base = 0;
@@ -259,7 +260,8 @@ int bpc_launch_schedule(bpc_context *ctx) {
     ctx->body_best.reserve(n, false, st);
     ctx->body_colmask.reserve(n, false, st);
     ctx->color_start.reserve(2 * (MAX_COLORS + 4), false, st);
-    if (np) k_con_collect<<<nblk(np, GR_THREADS), GR_THREADS, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->con_list.p, ctx->counters.p);
+    if (np) k_con_collect<<<nblk(np, GR_THREADS), GR_THREADS, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->pair_keys[ctx->cur].p, ctx->meta.p,
+                                                                        ctx->island.p, ctx->island_flag.p, ctx->con_list.p, ctx->counters.p);
     BPC_CHECK(cudaMemsetAsync(ctx->body_best.p, 0, (size_t)n * 8, st));
     BPC_CHECK(cudaMemsetAsync(ctx->body_colmask.p, 0, (size_t)n * 8, st));
     BPC_CHECK(cudaMemsetAsync(ctx->color_start.p, 0, 2 * (MAX_COLORS + 4) * sizeof(uint32_t), st));

@@ -308,6 +308,33 @@ def batched_worlds(n_spaces=4096, seed0=1000, lattice=(8, 4, 8)):
     return sc
 
 
+def convex_pile(n_side=4, n_hulls=8, seed=11, with_primitives=True):
+    """Convex-hull debris (C4's hulls, no joints) dropped on a plane, optionally mixed with
+    boxes / spheres / capsules so every hull-vs-primitive narrowphase pair occurs."""
+    sc = Scene(name="convex_pile_%d" % n_side ** 3)
+    _container(sc, n_side * 0.6 + 1.5)
+    rng = np.random.default_rng(seed)
+    hull_ids = []
+    for _ in range(n_hulls):
+        semi = rng.uniform(0.3, 0.6, 3)
+        d = rng.normal(size=(14, 3))
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        hull_ids.append(sc.add_shape(SHAPE_CONVEX, verts=(d * semi).astype(np.float32)))
+    prim = [sc.add_shape(SHAPE_BOX, (0.3, 0.25, 0.35)), sc.add_shape(SHAPE_SPHERE, (0.35,)), sc.add_shape(SHAPE_CAPSULE, (0.2, 1.0))]
+    n = n_side ** 3
+    g = np.stack(np.meshgrid(np.arange(n_side), np.arange(n_side), np.arange(n_side), indexing="ij"), -1).reshape(-1, 3)
+    pos = np.stack([(g[:, 0] - (n_side - 1) * 0.5) * 1.2, 1.0 + g[:, 1] * 1.2, (g[:, 2] - (n_side - 1) * 0.5) * 1.2], -1)
+    shape = np.array(hull_ids, np.uint32)[rng.integers(0, n_hulls, n)]
+    if with_primitives:
+        sel = np.arange(n) % 4 == 3
+        shape[sel] = np.array(prim, np.uint32)[rng.integers(0, 3, int(sel.sum()))]
+    xf = np.zeros((n, 12), np.float32)
+    xf[:, :9] = _random_rotations(rng, n)
+    xf[:, 9:12] = pos.astype(np.float32)
+    sc.add_bodies(n, shape=shape, xf=xf, mass=1.0, friction=1.0)
+    return sc
+
+
 def free_fall(n=64, seed=3):
     """Contact-free scene: tumbling mixed bodies far apart (integration parity)."""
     sc = Scene(name="free_fall_%d" % n)

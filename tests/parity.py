@@ -101,6 +101,54 @@ def rel_err(a, b, floor=1e-3):
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
 
 
+def teacher_forced(sc, steps, check_steps, import_order=True, dump=None):
+    """For each k in check_steps: load the oracle's state after step k into the GPU, take one step and
+    compare with the oracle's step k+1.  Pair set and colliding-pair list are asserted bit-exact here;
+    the worst contact / body-state errors are returned for the caller to bound.
+
+    Step 0 -> 1 is never checked: the reference flushes its pending shape updates at the start of the
+    first step (bradot_physics_server_3d.cpp:1728-1733), which re-stores every broadphase box before pairing."""
+    if dump is None:
+        _, dump = run_oracle(sc, steps, dump_from=0, dump_every=1)
+    ps = new_server(sc, dump)
+    worst = {"contact": 0.0, "state": 0.0, "pairs": 0, "colliding": 0, "contacts": 0}
+    for k in check_steps:
+        assert k >= 1
+        load_state(ps, dump, k)
+        if import_order:
+            ps.set_solve_order(solve_order(dump, k + 1))
+        ps.step(sc.dt)
+        st = ps.stats()
+        if import_order:
+            assert st["overflow"] == 0, "colliding pairs missing from the imported sweep order at step %d" % (k + 1)
+        ids, pf, cf = ps.pairs_read()
+        rids, rpf, rcf = oracle_pairs(dump, k + 1)
+        gk, rk = pair_keys(ids), pair_keys(rids)
+        order = np.argsort(rk)
+        assert np.array_equal(gk, rk[order]), "pair set differs at step %d: gpu %d ref %d" % (k + 1, len(gk), len(rk))
+        rids, rpf, rcf = rids[order], rpf[order], rcf[order]
+        # the reference only visits constraints reachable from awake bodies; compare those
+        awake = dump[("bodies", k)][:, 18] > 0
+        touched = awake[rids[:, 0]] | awake[rids[:, 1]]
+        assert np.array_equal((ids[:, 3] & 1)[touched], (rids[:, 3] & 1)[touched]), "colliding-pair list differs at step %d" % (k + 1)
+        assert np.array_equal(ids[touched, 2], rids[touched, 2]), "contact counts differ at step %d" % (k + 1)
+        for q in range(4):
+            m = touched & (rids[:, 2] > q)
+            worst["contact"] = max(worst["contact"], rel_err(cf[m, q, 0:9], rcf[m, q, 0:9], 1.0))
+            worst["contacts"] += int(m.sum())
+        worst["pairs"] += len(gk)
+        worst["colliding"] += int(((rids[:, 3] & 1) > 0)[touched].sum())
+        if import_order:
+            ref = dump[("bodies", k + 1)]
+            xf = ps.bodies_read(server.FIELD_TRANSFORM)
+            lv = ps.bodies_read(server.FIELD_LINEAR_VELOCITY)
+            av = ps.bodies_read(server.FIELD_ANGULAR_VELOCITY)
+            e = max(rel_err(xf, ref[:, 0:12], 1.0), rel_err(lv, ref[:, 12:15], 1.0), rel_err(av, ref[:, 15:18], 1.0))
+            worst["state"] = max(worst["state"], e)
+    ps.finish()
+    return worst
+
+
 def kinetic_energy_and_momentum(sc, bodies):
     """Translational kinetic energy and linear momentum of the dynamic bodies (mass from the scene)."""
     m = sc.bodies["mass"].astype(np.float64)
