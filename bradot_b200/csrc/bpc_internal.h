@@ -104,6 +104,17 @@ struct JointRec {
     float fa[12], fb[12];
 };
 
+// Per-step joint data written by k_joint_setup (the Jacobian diagonals of BradotJacobianEntry3D and
+// everything about the pivots / axes that stays constant while the solver sweeps).
+struct __align__(16) JointSetup {
+    float4 n0, n1, n2; // linear row directions xyz, w = 1 / Jacobian diagonal
+    float4 pa;         // pivot A in world minus origin A ; w = flags (bit0 dynamic_A, bit1 dynamic_B, bit2 awake)
+    float4 pb;         // pivot B in world minus origin B
+    float4 dpos;       // pivotAInW - pivotBInW
+    float4 axis_a;     // hinge axis of A in world
+    float4 axis_b;     // hinge axis of B in world
+};
+
 struct Stats {
     int active_objects, collision_pairs, island_count, contact_pairs, colors, contacts, overflow, steps;
 };
@@ -131,6 +142,7 @@ struct bpc_context {
     double stage_ms[BPC_N_STAGES] = {};
     uint32_t stage_steps = 0;
     DevBuf<JointRec> d_joints;
+    DevBuf<JointSetup> jsetup;
     DevBuf<uint64_t> forced_keys;
 
     uint32_t n_bodies = 0;
@@ -250,6 +262,7 @@ int bpc_launch_broadphase(bpc_context *ctx);
 int bpc_launch_islands(bpc_context *ctx);
 int bpc_launch_narrowphase(bpc_context *ctx);
 int bpc_launch_solver(bpc_context *ctx, float dt);
+int bpc_launch_joint_setup(bpc_context *ctx, float dt);
 int bpc_launch_sleep(bpc_context *ctx, float dt);
 // radix sort of 64-bit keys (+ optional 32-bit values) on the 8-bit digits that intersect `bitmask`;
 // result is left in *keys/*vals (the pointers are swapped with their alternates as needed)

@@ -25,6 +25,10 @@ __global__ void k_forced_lookup(uint32_t n, const uint64_t *__restrict__ fkeys, 
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint64_t key = fkeys[i];
+    if (key >> 63) { // joint: constraint id = n_pairs + joint index
+        order[i] = n_pairs + (uint32_t)key;
+        return;
+    }
     uint32_t lo = 0, hi = n_pairs;
     while (lo < hi) {
         uint32_t mid = (lo + hi) >> 1;
@@ -117,6 +121,7 @@ extern "C" int bpc_step(bpc_context *ctx, float dt) {
     if (bpc_launch_islands(ctx)) return -1;
     STAGE(3);
     if (bpc_launch_narrowphase(ctx)) return -1;
+    if (bpc_launch_joint_setup(ctx, dt)) return -1;
     uint32_t np = ctx->n_pairs[ctx->cur];
     if (np) {
         k_count_collided<<<nblk(np, 128), 128, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->counters.p);
@@ -275,8 +280,19 @@ extern "C" int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order
     std::vector<uint64_t> keys(n);
     uint32_t nlev = 0;
     for (int i = 0; i < n; i++) {
-        if (order[3 * i] != 0) return fail(ctx, "bpc_set_solve_order: only body-pair constraints (kind 0) can be ordered yet");
-        uint32_t a = (uint32_t)order[3 * i + 1], b = (uint32_t)order[3 * i + 2];
+        uint32_t a, b;
+        bool is_joint = order[3 * i] == 1;
+        if (is_joint) {
+            uint32_t j = (uint32_t)order[3 * i + 1];
+            if (j >= ctx->h_joints.size()) return fail(ctx, "bpc_set_solve_order: invalid joint index");
+            a = ctx->h_joints[j].a;
+            b = ctx->h_joints[j].b;
+        } else if (order[3 * i] == 0) {
+            a = (uint32_t)order[3 * i + 1];
+            b = (uint32_t)order[3 * i + 2];
+        } else {
+            return fail(ctx, "bpc_set_solve_order: unknown constraint kind");
+        }
         if (a >= ctx->n_bodies || b >= ctx->n_bodies) return fail(ctx, "bpc_set_solve_order: invalid body index");
         uint32_t l = 0;
         if (ctx->h_mode[a] > MODE_KINEMATIC) l = std::max(l, last[a]);
@@ -286,7 +302,7 @@ extern "C" int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order
         if (ctx->h_mode[a] > MODE_KINEMATIC) last[a] = l;
         if (ctx->h_mode[b] > MODE_KINEMATIC) last[b] = l;
         nlev = std::max(nlev, l);
-        keys[i] = ((uint64_t)std::min(a, b) << 32) | std::max(a, b);
+        keys[i] = is_joint ? ((1ull << 63) | (uint32_t)order[3 * i + 1]) : (((uint64_t)std::min(a, b) << 32) | std::max(a, b));
     }
     std::vector<uint32_t> start(nlev + 2, 0);
     for (int i = 0; i < n; i++) start[level[i]]++; // level l (1-based) counted at start[l]

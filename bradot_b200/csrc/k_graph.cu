@@ -77,12 +77,22 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_flatten(uint32_t n, uint32_t 
 }
 
 // island_count statistic: islands with at least one constraint (bradot_step_3d.cpp:292-294, 337)
+// islands held together by joints only have no pair on their root body: mark them
+__global__ void __launch_bounds__(GR_THREADS) k_island_joint_mark(uint32_t n, const JointRec *__restrict__ joints, const uint4 *__restrict__ meta,
+                                                                  const uint32_t *__restrict__ label, uint32_t *__restrict__ flag) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    uint32_t a = joints[j].a, b = joints[j].b;
+    uint32_t r = label[(meta[a].x & 0xffu) != MODE_STATIC ? a : b];
+    if (!(flag[r] & 8u)) atomicOr(&flag[r], 8u);
+}
+
 // A component of two or more bodies gives every member an edge, and a lone body's pairs all involve
 // it, so "island has a constraint" == "its root body has at least one pair".
 __global__ void __launch_bounds__(GR_THREADS) k_island_count(uint32_t n, const uint32_t *__restrict__ label, const uint32_t *__restrict__ flag,
                                                              const uint32_t *__restrict__ npairs, uint32_t *__restrict__ counters) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool isl = i < n && label[i] == i && (flag[i] & 1u) && npairs[i] > 0;
+    bool isl = i < n && label[i] == i && (flag[i] & 1u) && (npairs[i] > 0 || (flag[i] & 8u));
     uint32_t m = __ballot_sync(0xffffffffu, isl);
     if ((threadIdx.x & 31) == 0 && m) atomicAdd(&counters[CNT_ISLANDS], __popc(m));
 }
@@ -96,8 +106,9 @@ int bpc_launch_islands(bpc_context *ctx) {
     uint32_t nj = (uint32_t)ctx->h_joints.size();
     if (nj) k_cc_union_joints<<<nblk(nj, GR_THREADS), GR_THREADS, 0, st>>>(nj, ctx->d_joints.p, ctx->meta.p, ctx->island.p);
     k_cc_flatten<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->meta.p, ctx->island_flag.p);
+    if (nj) k_island_joint_mark<<<nblk(nj, GR_THREADS), GR_THREADS, 0, st>>>(nj, ctx->d_joints.p, ctx->meta.p, ctx->island.p, ctx->island_flag.p);
     k_island_count<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->island_flag.p, ctx->npairs.p, ctx->counters.p);
-    ctx->launches += 3 + (np ? 1 : 0) + (nj ? 1 : 0);
+    ctx->launches += 3 + (np ? 1 : 0) + (nj ? 2 : 0);
     BPC_CHECK(cudaGetLastError());
     return 0;
 }

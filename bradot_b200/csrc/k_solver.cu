@@ -32,6 +32,8 @@ struct SvArgs {
     uint32_t serial_group;       // index of a group that must run on one thread (colour overflow), or 0xffffffff
     uint4 *info;
     SolveContact *sc;
+    const JointRec *joints;
+    const JointSetup *jsetup;
     float dt, inv_dt, max_bias_av;
     int iterations;
     uint32_t *counters;
@@ -248,6 +250,180 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Joints: pin and hinge (modules/bradot_physics_3d/joints/bradot_pin_joint_3d.cpp:53-141,
+// joints/bradot_hinge_joint_3d.cpp:110-344, joints/bradot_jacobian_entry_3d.h:56-77).  Parameters are
+// the reference defaults: pin bias 0.3, damping 1, no clamp; hinge bias 0.3, relaxation 1, no limit, no motor.
+#define JOINT_TAU 0.3f
+#define JOINT_DAMPING 1.0f
+#define JOINT_RELAXATION 1.0f
+
+// BradotJoint3D::plane_space (bradot_joint_3d.h:43-59); Math_SQRT12 is a double
+__device__ __forceinline__ void plane_space(V3 n, V3 &p, V3 &q) {
+    if ((double)fabsf(n.z) > 0.7071067811865475244008443621048490) {
+        float a = n.y * n.y + n.z * n.z;
+        float k = (float)(1.0 / (double)sqrtf(a));
+        p = V3(0.f, -n.z * k, n.y * k);
+        q = V3(a * k, -n.x * p.z, n.x * p.y);
+    } else {
+        float a = n.x * n.x + n.y * n.y;
+        float k = (float)(1.0 / (double)sqrtf(a));
+        p = V3(-n.y * k, n.x * k, 0.f);
+        q = V3(-n.z * p.y, n.z * p.x, a * k);
+    }
+}
+
+// 1 / m_Adiag of the two-body linear Jacobian entry
+__device__ __forceinline__ float jac_diag_inv(const M3 &w2a, const M3 &w2b, V3 rel1, V3 rel2, V3 axis, V3 iiA, float imA, V3 iiB, float imB) {
+    V3 aJ = xform(w2a, cross(rel1, axis));
+    V3 bJ = xform(w2b, cross(rel2, -axis));
+    V3 m0(iiA.x * aJ.x, iiA.y * aJ.y, iiA.z * aJ.z);
+    V3 m1(iiB.x * bJ.x, iiB.y * bJ.y, iiB.z * bJ.z);
+    float adiag = imA + dot(m0, aJ) + imB + dot(m1, bJ);
+    return 1.0f / adiag;
+}
+
+struct JsArgs {
+    uint32_t n;
+    const JointRec *joints;
+    JointSetup *out;
+    const BodyXf *xf;
+    const BodyMassW *massw;
+    const BodyProps *props;
+    const uint4 *meta;
+    const uint32_t *island;
+    const uint32_t *island_flag;
+};
+
+__global__ void __launch_bounds__(128) k_joint_setup(JsArgs a) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= a.n) return;
+    const JointRec jr = a.joints[j];
+    uint32_t ma = a.meta[jr.a].x & 0xffu, mb = a.meta[jr.b].x & 0xffu;
+    bool dynA = ma > MODE_KINEMATIC, dynB = mb > MODE_KINEMATIC;
+    uint32_t root = a.island[ma != MODE_STATIC ? jr.a : jr.b];
+    bool awake = (ma != MODE_STATIC || mb != MODE_STATIC) && (a.island_flag[root] & 1u);
+    JointSetup s;
+    uint32_t flags = (dynA ? 1u : 0u) | (dynB ? 2u : 0u) | (awake ? 4u : 0u);
+    BodyXf xa = a.xf[jr.a], xb = a.xf[jr.b];
+    X3 XA(M3(f4v(xa.r0), f4v(xa.r1), f4v(xa.r2)), f4v(xa.o)), XB(M3(f4v(xb.r0), f4v(xb.r1), f4v(xb.r2)), f4v(xb.o));
+    BodyMassW mwa = a.massw[jr.a], mwb = a.massw[jr.b];
+    BodyProps pa = a.props[jr.a], pb = a.props[jr.b];
+    V3 comA(mwa.i0.w, mwa.i1.w, mwa.i2.w), comB(mwb.i0.w, mwb.i1.w, mwb.i2.w);
+    M3 w2a = transposed(XA.b * M3(f4v(pa.a0), f4v(pa.a1), f4v(pa.a2)));
+    M3 w2b = transposed(XB.b * M3(f4v(pb.a0), f4v(pb.a1), f4v(pb.a2)));
+    V3 iiA = f4v(pa.iinv_gs), iiB = f4v(pb.iinv_gs);
+    float imA = mwa.m.x, imB = mwb.m.x;
+    V3 pivA = xform(XA, V3(jr.fa[9], jr.fa[10], jr.fa[11]));
+    V3 pivB = xform(XB, V3(jr.fb[9], jr.fb[10], jr.fb[11]));
+    V3 rel1 = pivA - XA.o - comA, rel2 = pivB - XB.o - comB;
+    V3 nrm[3];
+    s.axis_a = make_float4(0.f, 0.f, 0.f, 0.f);
+    s.axis_b = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (jr.type == 0) {
+        nrm[0] = V3(1.f, 0.f, 0.f);
+        nrm[1] = V3(0.f, 1.f, 0.f);
+        nrm[2] = V3(0.f, 0.f, 1.f);
+    } else {
+        V3 relPos = pivB - pivA;
+        if (is_zero_approx(length_squared(relPos))) nrm[0] = V3(1.0f, 0.f, 0.f);
+        else nrm[0] = normalized(relPos);
+        plane_space(nrm[0], nrm[1], nrm[2]);
+        // hinge axes: column 2 of the local frames; B's column is flipped by the joint's constructor
+        V3 axA = xform(XA.b, V3(jr.fa[2], jr.fa[5], jr.fa[8]));
+        V3 axB = xform(XB.b, V3(jr.fb[2] * -1.f, jr.fb[5] * -1.f, jr.fb[8] * -1.f));
+        s.axis_a = v4(axA, 0.f);
+        s.axis_b = v4(axB, 0.f);
+    }
+    float d[3];
+    for (int i = 0; i < 3; i++) d[i] = jac_diag_inv(w2a, w2b, rel1, rel2, nrm[i], iiA, imA, iiB, imB);
+    s.n0 = v4(nrm[0], d[0]);
+    s.n1 = v4(nrm[1], d[1]);
+    s.n2 = v4(nrm[2], d[2]);
+    s.pa = v4(pivA - XA.o, __uint_as_float(flags));
+    s.pb = v4(pivB - XB.o, 0.f);
+    s.dpos = v4(pivA - pivB, 0.f);
+    a.out[j] = s;
+}
+
+__device__ __forceinline__ float ang_denominator(const BodyS &b, V3 axis) { // compute_angular_impulse_denominator
+    return dot(axis, xform_inv(b.iinv, axis));
+}
+
+__device__ inline void solve_joint(const SvArgs &a, uint32_t s) {
+    uint4 inf = a.info[s];
+    const JointSetup js = a.jsetup[inf.w];
+    uint32_t flags = __float_as_uint(js.pa.w);
+    if (!(flags & 4u)) return;
+    bool dynA = flags & 1u, dynB = flags & 2u;
+    if (!dynA && !dynB) return;
+    BodyS A, B;
+    float f0, f1, f2, f3;
+    load_body(a, inf.x, true, A, f0, f1);
+    load_body(a, inf.y, true, B, f2, f3);
+    V3 pA = f4v(js.pa), pB = f4v(js.pb), dpos = f4v(js.dpos);
+    const float4 rows[3] = { js.n0, js.n1, js.n2 };
+    uint32_t type = inf.z >> 16;
+    if (type == 0) { // pin: the relative velocity is re-read for every axis
+        for (int i = 0; i < 3; i++) {
+            V3 normal = f4v(rows[i]);
+            float jinv = rows[i].w;
+            V3 vel1 = A.lin + cross(A.ang, pA - A.com);
+            V3 vel2 = B.lin + cross(B.ang, pB - B.com);
+            V3 vel = vel1 - vel2;
+            float rel_vel = dot(normal, vel);
+            float depth = -dot(dpos, normal);
+            float impulse = depth * JOINT_TAU / a.dt * jinv - JOINT_DAMPING * rel_vel * jinv;
+            V3 iv = normal * impulse;
+            if (dynA) apply_impulse(A, iv, pA);
+            if (dynB) apply_impulse(B, -iv, pB);
+        }
+    } else { // hinge: one velocity sample for the three linear rows
+        V3 vel1 = A.lin + cross(A.ang, pA - A.com);
+        V3 vel2 = B.lin + cross(B.ang, pB - B.com);
+        V3 vel = vel1 - vel2;
+        for (int i = 0; i < 3; i++) {
+            V3 normal = f4v(rows[i]);
+            float jinv = rows[i].w;
+            float rel_vel = dot(normal, vel);
+            float depth = -dot(dpos, normal);
+            float impulse = depth * JOINT_TAU / a.dt * jinv - rel_vel * jinv;
+            V3 iv = normal * impulse;
+            if (dynA) apply_impulse(A, iv, pA);
+            if (dynB) apply_impulse(B, -iv, pB);
+        }
+        V3 axisA = f4v(js.axis_a), axisB = f4v(js.axis_b);
+        V3 angVelA = A.ang, angVelB = B.ang;
+        V3 aroundA = axisA * dot(axisA, angVelA);
+        V3 aroundB = axisB * dot(axisB, angVelB);
+        V3 angAorthog = angVelA - aroundA;
+        V3 angBorthog = angVelB - aroundB;
+        V3 velrelOrthog = angAorthog - angBorthog;
+        float len = length(velrelOrthog);
+        if (len > 0.00001f) {
+            V3 normal = normalized(velrelOrthog);
+            float denom = ang_denominator(A, normal) + ang_denominator(B, normal);
+            velrelOrthog *= (1.0f / denom) * JOINT_RELAXATION;
+        }
+        V3 angularError = -cross(axisA, axisB) * (1.0f / a.dt);
+        float len2 = length(angularError);
+        if (len2 > 0.00001f) {
+            V3 normal2 = normalized(angularError);
+            float denom2 = ang_denominator(A, normal2) + ang_denominator(B, normal2);
+            angularError *= (1.0f / denom2) * 1.0f;
+        }
+        if (dynA) A.ang += xform(A.iinv, -velrelOrthog + angularError);
+        if (dynB) B.ang += xform(B.iinv, velrelOrthog - angularError);
+    }
+    if (dynA) store_body(a, inf.x, A);
+    if (dynB) store_body(a, inf.y, B);
+}
+
+__device__ inline void pre_solve_joint(const SvArgs &a, uint32_t s, uint32_t j) {
+    const JointRec &jr = a.joints[j];
+    a.info[s] = make_uint4(jr.a, jr.b, 0x1000u | (jr.type << 16), j);
+}
+
 __device__ inline void finish_pair(const SvArgs &a, uint32_t s) {
     uint4 inf = a.info[s];
     int count = inf.z & 0xffu;
@@ -273,12 +449,14 @@ __global__ void __launch_bounds__(SV_THREADS) k_solve(SvArgs a) {
                 for (uint32_t s = lo; s < hi; s++) {
                     uint32_t id = a.sched[s];
                     if (id < a.n_pairs) pre_solve_pair(a, s, id);
+                    else if (id != 0xffffffffu) pre_solve_joint(a, s, id - a.n_pairs);
                 }
             }
         } else {
             for (uint32_t s = lo + tid; s < hi; s += nth) {
                 uint32_t id = a.sched[s];
                 if (id < a.n_pairs) pre_solve_pair(a, s, id);
+                else if (id != 0xffffffffu) pre_solve_joint(a, s, id - a.n_pairs);
             }
         }
         grid.sync();
@@ -289,12 +467,16 @@ __global__ void __launch_bounds__(SV_THREADS) k_solve(SvArgs a) {
             if (g == a.serial_group) {
                 if (tid == 0) {
                     for (uint32_t s = lo; s < hi; s++) {
-                        if (a.sched[s] < a.n_pairs) solve_pair(a, s);
+                        uint32_t id = a.sched[s];
+                        if (id < a.n_pairs) solve_pair(a, s);
+                        else if (id != 0xffffffffu) solve_joint(a, s);
                     }
                 }
             } else {
                 for (uint32_t s = lo + tid; s < hi; s += nth) {
-                    if (a.sched[s] < a.n_pairs) solve_pair(a, s);
+                    uint32_t id = a.sched[s];
+                    if (id < a.n_pairs) solve_pair(a, s);
+                    else if (id != 0xffffffffu) solve_joint(a, s);
                 }
             }
             grid.sync();
@@ -304,6 +486,30 @@ __global__ void __launch_bounds__(SV_THREADS) k_solve(SvArgs a) {
     for (uint32_t s = tid; s < total; s += nth) {
         if (a.sched[s] < a.n_pairs) finish_pair(a, s);
     }
+}
+
+int bpc_launch_joint_setup(bpc_context *ctx, float dt) {
+    uint32_t nj = (uint32_t)ctx->h_joints.size();
+    if (!nj) return 0;
+    ctx->jsetup.reserve(nj, false, ctx->stream);
+    if (!ctx->jsetup.p) {
+        ctx->err = "joints: out of device memory";
+        return -1;
+    }
+    JsArgs a;
+    a.n = nj;
+    a.joints = ctx->d_joints.p;
+    a.out = ctx->jsetup.p;
+    a.xf = ctx->xf.p;
+    a.massw = ctx->massw.p;
+    a.props = ctx->props.p;
+    a.meta = ctx->meta.p;
+    a.island = ctx->island.p;
+    a.island_flag = ctx->island_flag.p;
+    k_joint_setup<<<(nj + 127) / 128, 128, 0, ctx->stream>>>(a);
+    ctx->launches += 1;
+    BPC_CHECK(cudaGetLastError());
+    return 0;
 }
 
 int bpc_launch_solver(bpc_context *ctx, float dt) {
@@ -342,6 +548,8 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     }
     a.info = ctx->con_info.p;
     a.sc = ctx->scontacts.p;
+    a.joints = ctx->d_joints.p;
+    a.jsetup = ctx->jsetup.p;
     a.dt = dt;
     a.inv_dt = (float)(1.0 / (double)dt);
     a.max_bias_av = (float)((3.14159265358979323846 / 8) / (double)dt);

@@ -74,8 +74,7 @@ def solve_order(dump, step):
     ids = dump[("pair_ids", step)]
     out = np.zeros((len(so), 3), np.int32)
     for i, (isl, kind, idx) in enumerate(so):
-        assert kind == 0
-        out[i] = (0, ids[idx, 0], ids[idx, 1])
+        out[i] = (0, ids[idx, 0], ids[idx, 1]) if kind == 0 else (1, idx, 0)
     return out
 
 

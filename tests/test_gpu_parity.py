@@ -119,3 +119,12 @@ def test_free_run_energy_and_momentum_600_steps(name, tol):
         assert abs(e1 - e2) <= tol * e_scale, (name, e1, e2)
         assert np.max(np.abs(p1 - p2)) <= tol * max(p_scale, float(np.max(np.abs(p2)))), (name, p1, p2)
     ps.finish()
+
+
+def test_teacher_forced_joint_chains():     # pin + hinge chains of convex hulls (C4 layout), linked bodies excepted from colliding
+    _need_oracle()
+    sc = scenes.convex_chains(n_chains=9, chain_len=5, n_hulls=4)
+    w = parity.teacher_forced(sc, 120, [1, 20, 40, 60, 80, 100, 119])
+    assert w["contact"] < CONTACT_TOL, w
+    assert w["state"] < STATE_TOL, w
+    assert w["colliding"] > 0
