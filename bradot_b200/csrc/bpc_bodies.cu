@@ -174,7 +174,7 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
     }
     if (!grow(ctx, ctx->xf, total) || !grow(ctx, ctx->shape_xf, total) || !grow(ctx, ctx->vel, total) || !grow(ctx, ctx->massw, total) ||
         !grow(ctx, ctx->props, total) || !grow(ctx, ctx->forces, total) || !grow(ctx, ctx->meta, total) || !grow(ctx, ctx->shape_id, total) ||
-        !grow(ctx, ctx->items, total) || !grow(ctx, ctx->npairs, total) || !grow(ctx, ctx->island, total) || !grow(ctx, ctx->island_flag, total))
+        !grow(ctx, ctx->shape_p, total) || !grow(ctx, ctx->items, total) || !grow(ctx, ctx->npairs, total) || !grow(ctx, ctx->island, total) || !grow(ctx, ctx->island_flag, total))
         return fail(ctx, "bpc_bodies_create: out of device memory");
     if (bpc_flush_tables(ctx)) return -1;
     std::vector<BodyXf> xf(n), sxf(n);
@@ -183,6 +183,7 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
     std::vector<BodyProps> props(n);
     std::vector<uint4> meta(n);
     std::vector<uint32_t> sid(n);
+    std::vector<float4> sp(n);
     ctx->h_mode.resize(total);
     ctx->h_big.resize(total);
     for (int i = 0; i < n; i++) {
@@ -200,7 +201,13 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
         mw[i].m = make_float4(inv_mass, d.friction, d.bounce, 0.f);
         uint32_t flags = (d.flags & 1u ? BF_CAN_SLEEP : 0u) | (d.flags & 4u ? 0u : BF_ACTIVE);
         if (d.mode == MODE_STATIC) flags &= ~BF_ACTIVE;
-        meta[i] = make_uint4(d.mode | (flags << 8), d.layer, d.mask, d.space);
+        bool ident = true;
+        for (int q = 0; q < 12; q++) ident = ident && d.shape_xf[q] == ((q == 0 || q == 4 || q == 8) ? 1.f : 0.f);
+        if (ident) flags |= BF_SHAPE_IDENT;
+        meta[i] = make_uint4(d.mode | (flags << 8) | (sh.meta.x << 24), d.layer, d.mask, d.space);
+        sp[i] = sh.p;
+        ctx->shape_type_mask |= 1u << sh.meta.x;
+        if (sh.meta.x == SH_CONVEX) memcpy(&sp[i].x, &sh.meta.y, 4);
         sid[i] = d.shape;
         ctx->h_mode[first + i] = (uint8_t)d.mode;
         ctx->h_big[first + i] = (d.mode == MODE_STATIC && sh.meta.x == SH_PLANE) ? 1 : 0;
@@ -213,6 +220,7 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
     BPC_CHECK(cudaMemcpyAsync(ctx->props.p + first, props.data(), n * sizeof(BodyProps), cudaMemcpyHostToDevice, st));
     BPC_CHECK(cudaMemcpyAsync(ctx->meta.p + first, meta.data(), n * sizeof(uint4), cudaMemcpyHostToDevice, st));
     BPC_CHECK(cudaMemcpyAsync(ctx->shape_id.p + first, sid.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    BPC_CHECK(cudaMemcpyAsync(ctx->shape_p.p + first, sp.data(), n * sizeof(float4), cudaMemcpyHostToDevice, st));
     BPC_CHECK(cudaMemsetAsync(ctx->forces.p + first, 0, n * sizeof(BodyForces), st));
     BPC_CHECK(cudaMemsetAsync(ctx->items.p + first, 0, n * sizeof(ItemBox), st));
     BPC_CHECK(cudaMemsetAsync(ctx->npairs.p + first, 0, n * sizeof(uint32_t), st));

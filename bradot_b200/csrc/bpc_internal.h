@@ -20,6 +20,9 @@ enum { MODE_STATIC = 0, MODE_KINEMATIC = 1, MODE_RIGID = 2, MODE_RIGID_LINEAR = 
 #define BF_ACTIVE 4u
 #define BF_OMIT_FORCE 8u
 #define BF_LOCK_SHIFT 8 // 6 axis-lock bits, same order as PhysicsServer3D::BodyAxis
+#define BF_SHAPE_IDENT (1u << 14)  // the shape's local transform is the identity (no product needed)
+#define BF_ISLAND_AWAKE (1u << 15) // refreshed every step: the body's island holds an awake body
+// meta.x bits 24..31: shape type of the body's shape (copy of ShapeRec.meta.x, saves a dependent gather)
 
 // 64-byte records: one gather = two 32-byte sectors, all of it used.
 struct __align__(16) BodyXf {
@@ -143,6 +146,7 @@ struct bpc_context {
     uint32_t stage_steps = 0;
     DevBuf<JointRec> d_joints;
     DevBuf<JointSetup> jsetup;
+    DevBuf<uint32_t> np_work; // broadphase pairs that need the full narrowphase pass this step
     DevBuf<uint64_t> forced_keys;
 
     uint32_t n_bodies = 0;
@@ -154,6 +158,7 @@ struct bpc_context {
     DevBuf<BodyForces> forces;
     DevBuf<uint4> meta; // mode|flags<<8, layer, mask, space
     DevBuf<uint32_t> shape_id;
+    DevBuf<float4> shape_p;    // per-body copy of the shape parameters (convex: x = mesh index bits)
     DevBuf<ItemBox> items;
     DevBuf<uint32_t> npairs;   // pairs per item after the last broadphase update (drives the margin)
     DevBuf<uint32_t> tree_items; // body ids that live in the LBVH (everything except unbounded statics)
@@ -196,6 +201,7 @@ struct bpc_context {
     std::vector<uint64_t> h_except;
     uint32_t n_except = 0;
     bool except_dirty = false;
+    uint32_t shape_type_mask = 0; // shape types present among the bodies (bit = ShapeType)
     std::vector<uint8_t> h_big;  // 1 = unbounded static item (world boundary), kept out of the LBVH
     std::vector<uint8_t> h_mode; // host mirror of the body modes (scheduling of teacher-forced sweeps)
 
@@ -219,7 +225,7 @@ struct bpc_context {
 };
 
 enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIVE = 4, CNT_ISLANDS = 5, CNT_CONTACTS = 6,
-       CNT_OVERFLOW = 7, CNT_ROUND = 8, CNT_ACTIVE_CONTACTS = 10, CNT_N = 16 };
+       CNT_OVERFLOW = 7, CNT_ROUND = 8, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_N = 16 };
 
 #define BPC_CHECK(x)                                                                                  \
     do {                                                                                              \

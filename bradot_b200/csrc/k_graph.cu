@@ -76,6 +76,16 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_flatten(uint32_t n, uint32_t 
     if ((m & 0xffu) != MODE_STATIC && ((m >> 8) & BF_ACTIVE)) atomicOr(&flag[r], 1u); // island holds an awake body
 }
 
+// per-body copy of "my island is awake" so that pair kernels need no label/flag gathers
+__global__ void __launch_bounds__(GR_THREADS) k_island_bits(uint32_t n, const uint32_t *__restrict__ label, const uint32_t *__restrict__ flag,
+                                                           uint4 *__restrict__ meta) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t m = meta[i].x;
+    uint32_t want = (flag[label[i]] & 1u) ? (m | (BF_ISLAND_AWAKE << 8)) : (m & ~(BF_ISLAND_AWAKE << 8));
+    if (want != m) meta[i].x = want;
+}
+
 // island_count statistic: islands with at least one constraint (bradot_step_3d.cpp:292-294, 337)
 // islands held together by joints only have no pair on their root body: mark them
 __global__ void __launch_bounds__(GR_THREADS) k_island_joint_mark(uint32_t n, const JointRec *__restrict__ joints, const uint4 *__restrict__ meta,
@@ -106,9 +116,10 @@ int bpc_launch_islands(bpc_context *ctx) {
     uint32_t nj = (uint32_t)ctx->h_joints.size();
     if (nj) k_cc_union_joints<<<nblk(nj, GR_THREADS), GR_THREADS, 0, st>>>(nj, ctx->d_joints.p, ctx->meta.p, ctx->island.p);
     k_cc_flatten<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->meta.p, ctx->island_flag.p);
+    k_island_bits<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->island_flag.p, ctx->meta.p);
     if (nj) k_island_joint_mark<<<nblk(nj, GR_THREADS), GR_THREADS, 0, st>>>(nj, ctx->d_joints.p, ctx->meta.p, ctx->island.p, ctx->island_flag.p);
     k_island_count<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->island_flag.p, ctx->npairs.p, ctx->counters.p);
-    ctx->launches += 3 + (np ? 1 : 0) + (nj ? 2 : 0);
+    ctx->launches += 4 + (np ? 1 : 0) + (nj ? 2 : 0);
     BPC_CHECK(cudaGetLastError());
     return 0;
 }

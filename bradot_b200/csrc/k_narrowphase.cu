@@ -1,5 +1,9 @@
 // Constraint setup for every broadphase pair of an awake island: filters, stale-contact removal,
-// shape-vs-shape test and persistent manifold update.  One thread per pair over the sorted pair list.
+// shape-vs-shape test and persistent manifold update, in two passes so that warps stay uniform:
+//   k_pair_test   one lean thread per broadphase pair: filters + the separating-axis DECISION only
+//                 (registers, no manifold); pairs that collide or still hold cached contacts are compacted
+//   k_pair_setup  one thread per surviving pair: stale-contact removal, full SAT with contact generation,
+//                 manifold update.  Most broadphase pairs are box-overlap-only and never reach it.
 //   modules/bradot_physics_3d/bradot_body_pair_3d.cpp:264-317  BradotBodyPair3D::setup
 //   modules/bradot_physics_3d/bradot_step_3d.cpp:347-349       parallel _setup_constraint over all constraints
 #include "np_sat.cuh"
@@ -16,6 +20,7 @@ struct NpArgs {
     const BodyXf *shape_xf;
     const uint4 *meta;
     const uint32_t *shape_id;
+    const float4 *shape_p;
     const ShapeRec *shapes;
     const MeshRec *meshes;
     const float4 *mverts;
@@ -29,6 +34,9 @@ struct NpArgs {
     const uint64_t *except_keys;
     uint32_t n_except;
     uint32_t *counters;
+    uint32_t *work;      // compacted pair indices for the full pass
+    const uint32_t *perm; // pair indices binned by shape-type pair (nullptr = identity)
+    uint32_t n_work;
 };
 
 __device__ __forceinline__ Sh load_shape(const NpArgs &a, uint32_t sid) {
@@ -53,37 +61,113 @@ __device__ __forceinline__ Sh load_shape(const NpArgs &a, uint32_t sid) {
 
 __device__ __forceinline__ X3 load_xf(const BodyXf &x) { return X3(M3(f4v(x.r0), f4v(x.r1), f4v(x.r2)), f4v(x.o)); }
 
-__global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
+// shape from the per-body copies: type from meta.x bits 24..31, parameters from shape_p
+__device__ __forceinline__ Sh load_shape_fast(const NpArgs &a, uint32_t body, uint32_t meta_x) {
+    Sh s;
+    s.type = meta_x >> 24;
+    s.p = a.shape_p[body];
+    s.m.nv = s.m.nf = s.m.ne = 0;
+    if (s.type == SH_CONVEX) {
+        MeshRec m = a.meshes[__float_as_uint(s.p.x)];
+        s.m.verts = a.mverts + m.vert_ofs;
+        s.m.planes = a.mplanes + m.face_ofs;
+        s.m.edges = a.medges + m.edge_ofs;
+        s.m.faces = a.mfaces + m.face_ofs;
+        s.m.index = a.mindex;
+        s.m.nv = m.vert_cnt;
+        s.m.nf = m.face_cnt;
+        s.m.ne = m.edge_cnt;
+    }
+    return s;
+}
+// world transform of a body's shape relative to A's origin; multiplying by an identity local transform is exact,
+// so the product is skipped when the flag says so
+__device__ __forceinline__ X3 shape_world(const NpArgs &a, uint32_t body, uint32_t meta_x, const M3 &basis, V3 origin) {
+    if ((meta_x >> 8) & BF_SHAPE_IDENT) return X3(basis, origin);
+    return X3(basis, origin) * load_xf(a.shape_xf[body]);
+}
+
+// Bin key of a pair: the (unordered) pair of shape types, so that a warp runs one collision routine.
+__global__ void __launch_bounds__(256) k_type_keys(uint32_t n, const uint64_t *__restrict__ keys, const uint4 *__restrict__ meta,
+                                                   uint64_t *__restrict__ tkeys, uint32_t *__restrict__ vals) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= a.n_pairs) return;
+    if (k >= n) return;
+    uint64_t key = keys[k];
+    uint32_t ta = meta[(uint32_t)(key >> 32)].x >> 24, tb = meta[(uint32_t)key].x >> 24;
+    tkeys[k] = (uint64_t)(min(ta, tb) * 8u + max(ta, tb));
+    vals[k] = k;
+}
+
+__global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    bool work = false;
+    if (t < a.n_pairs) {
+        uint32_t k = a.perm ? a.perm[t] : t;
+        uint64_t key = a.keys[k];
+        uint32_t ia = (uint32_t)(key >> 32), ib = (uint32_t)key;
+        uint4 ma = a.meta[ia], mb = a.meta[ib];
+        uint32_t mode_a = ma.x & 0xffu, mode_b = mb.x & 0xffu;
+        // constraints are only visited from awake islands (bradot_step_3d.cpp:264-299)
+        if (((mode_a != MODE_STATIC ? ma.x : mb.x) >> 8) & BF_ISLAND_AWAKE) {
+            PairHdr h = a.hdr[k];
+            uint32_t bits = __float_as_uint(h.sep.w);
+            uint32_t count = bits & 0xffu;
+            bool interacts = (ma.y & mb.z) || (mb.y & ma.z);
+            bool excepted = false;
+            if (a.n_except) {
+                uint32_t lo = 0, hi = a.n_except;
+                while (lo < hi) {
+                    uint32_t mid = (lo + hi) >> 1;
+                    if (a.except_keys[mid] < key) lo = mid + 1;
+                    else hi = mid;
+                }
+                excepted = lo < a.n_except && a.except_keys[lo] == key;
+            }
+            bool collide_A = (mode_a > MODE_KINEMATIC) && (mb.y & ma.z);
+            bool collide_B = (mode_b > MODE_KINEMATIC) && (ma.y & mb.z);
+            uint32_t nb = count; // collided = false, contacts untouched
+            if (interacts && !excepted && (collide_A || collide_B)) {
+                BodyXf bxa = a.xf[ia], bxb = a.xf[ib];
+                M3 bA(f4v(bxa.r0), f4v(bxa.r1), f4v(bxa.r2)), bB(f4v(bxb.r0), f4v(bxb.r1), f4v(bxb.r2));
+                V3 offset_B = f4v(bxb.o) - f4v(bxa.o);
+                X3 xA = shape_world(a, ia, ma.x, bA, V3());
+                X3 xB = shape_world(a, ib, mb.x, bB, offset_B);
+                Sh sa = load_shape_fast(a, ia, ma.x);
+                Sh sb = load_shape_fast(a, ib, mb.x);
+                V3 sep_axis = f4v(h.sep);
+                Manifold *none = nullptr;
+                bool collided = solve_static<true>(sa, xA, sb, xB, *none, &sep_axis);
+                nb |= (collide_A ? 0x200u : 0u) | (collide_B ? 0x400u : 0u);
+                // the full pass decides again and generates contacts; cached contacts must be validated even when apart
+                work = collided || count > 0;
+            }
+            if (!work) {
+                h.sep.w = __uint_as_float(nb);
+                a.hdr[k] = h;
+            }
+        }
+    }
+    uint32_t m = __ballot_sync(0xffffffffu, work);
+    if (!m) return;
+    uint32_t lane = threadIdx.x & 31, base = 0;
+    if (lane == 0) base = atomicAdd(&a.counters[CNT_WORK], __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (work) a.work[base + __popc(m & ((1u << lane) - 1u))] = a.perm ? a.perm[t] : t;
+}
+
+__global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
+    uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= a.counters[CNT_WORK]) return;
+    uint32_t k = a.work[w];
     uint64_t key = a.keys[k];
     uint32_t ia = (uint32_t)(key >> 32), ib = (uint32_t)key;
     uint4 ma = a.meta[ia], mb = a.meta[ib];
     uint32_t mode_a = ma.x & 0xffu, mode_b = mb.x & 0xffu;
-    // constraints are only visited from awake islands (bradot_step_3d.cpp:264-299)
-    uint32_t root = a.island[mode_a != MODE_STATIC ? ia : ib];
-    if (!(a.island_flag[root] & 1u)) return;
     PairHdr h = a.hdr[k];
     uint32_t bits = __float_as_uint(h.sep.w);
     int count = bits & 0xffu;
-    bool interacts = (ma.y & mb.z) || (mb.y & ma.z);
-    bool excepted = false;
-    if (a.n_except) {
-        uint32_t lo = 0, hi = a.n_except;
-        while (lo < hi) {
-            uint32_t mid = (lo + hi) >> 1;
-            if (a.except_keys[mid] < key) lo = mid + 1;
-            else hi = mid;
-        }
-        excepted = lo < a.n_except && a.except_keys[lo] == key;
-    }
     bool collide_A = (mode_a > MODE_KINEMATIC) && (mb.y & ma.z);
     bool collide_B = (mode_b > MODE_KINEMATIC) && (ma.y & mb.z);
-    if (!interacts || excepted || (!collide_A && !collide_B)) {
-        h.sep.w = __uint_as_float((uint32_t)count); // collided = false, contacts untouched
-        a.hdr[k] = h;
-        return;
-    }
     BodyXf bxa = a.xf[ia], bxb = a.xf[ib];
     const SpaceParams sp = a.spaces[ma.w];
     Manifold m;
@@ -107,12 +191,12 @@ __global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
         }
     }
     manifold_validate(m, sp.max_separation);
-    X3 xA = X3(m.bA, V3()) * load_xf(a.shape_xf[ia]);
-    X3 xB = X3(m.bB, m.offset_B) * load_xf(a.shape_xf[ib]);
-    Sh sa = load_shape(a, a.shape_id[ia]);
-    Sh sb = load_shape(a, a.shape_id[ib]);
+    X3 xA = shape_world(a, ia, ma.x, m.bA, V3());
+    X3 xB = shape_world(a, ib, mb.x, m.bB, m.offset_B);
+    Sh sa = load_shape_fast(a, ia, ma.x);
+    Sh sb = load_shape_fast(a, ib, mb.x);
     V3 sep_axis = f4v(h.sep);
-    bool collided = solve_static(sa, xA, sb, xB, m, &sep_axis);
+    bool collided = solve_static<false>(sa, xA, sb, xB, m, &sep_axis);
     for (int c = 0; c < m.count; c++) {
         ContactGeo g;
         g.la = v4(m.la[c], __uint_as_float(m.used[c] ? 1u : 0u));
@@ -142,6 +226,7 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
     a.shape_xf = ctx->shape_xf.p;
     a.meta = ctx->meta.p;
     a.shape_id = ctx->shape_id.p;
+    a.shape_p = ctx->shape_p.p;
     a.shapes = ctx->shapes.p;
     a.meshes = ctx->meshes.p;
     a.mverts = ctx->mverts.p;
@@ -155,8 +240,34 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
     a.except_keys = ctx->except_keys.p;
     a.n_except = ctx->n_except;
     a.counters = ctx->counters.p;
+    ctx->np_work.reserve((size_t)n + 1, false, ctx->stream);
+    if (!ctx->np_work.p) {
+        ctx->err = "narrowphase: out of device memory";
+        return -1;
+    }
+    a.work = ctx->np_work.p;
+    a.n_work = 0;
+    a.perm = nullptr;
+    uint32_t solid_types = ctx->shape_type_mask & ~(1u << SH_PLANE);
+    if (solid_types & (solid_types - 1)) { // more than one kind of solid shape: bin the pairs by type pair
+        cudaStream_t st = ctx->stream;
+        ctx->keys.reserve(n, false, st);
+        ctx->keys_alt.reserve(n, false, st);
+        ctx->vals.reserve(n, false, st);
+        ctx->vals_alt.reserve(n, false, st);
+        if (!ctx->keys.p || !ctx->keys_alt.p || !ctx->vals.p || !ctx->vals_alt.p) {
+            ctx->err = "narrowphase: out of device memory";
+            return -1;
+        }
+        k_type_keys<<<(n + 255) / 256, 256, 0, st>>>(n, a.keys, a.meta, ctx->keys.p, ctx->vals.p);
+        ctx->launches += 1;
+        if (bpc_radix_sort(ctx, &ctx->keys.p, &ctx->keys_alt.p, &ctx->vals.p, &ctx->vals_alt.p, n, 0xffull)) return -1;
+        a.perm = ctx->vals.p;
+    }
+    k_pair_test<<<(n + 127) / 128, 128, 0, ctx->stream>>>(a);
+    // the survivor count stays on the device: launch for the worst case, surplus threads exit at once
     k_pair_setup<<<(n + NP_THREADS - 1) / NP_THREADS, NP_THREADS, 0, ctx->stream>>>(a);
-    ctx->launches += 1;
+    ctx->launches += 2;
     BPC_CHECK(cudaGetLastError());
     return 0;
 }

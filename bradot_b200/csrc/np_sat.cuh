@@ -50,8 +50,16 @@ struct Separator {
         if (cb->prev_axis && !(*cb->prev_axis == V3())) return test_axis(*cb->prev_axis);
         return true;
     }
+    // TEST = decide "colliding or not" only: same axis tests and early-outs, no contact generation and no
+    // write to the cached axis (what the reference does when no result callback is given, ...sat.cpp:710-717,
+    // minus the axis store, which the full pass performs).
+    template <bool TEST>
     __device__ inline void generate_contacts() {
         if (best_axis == V3(0.f, 0.f, 0.f)) return;
+        if (TEST) {
+            cb->collided = true;
+            return;
+        }
         V3 sA[MAX_SUPPORTS], sB[MAX_SUPPORTS];
         int nA, nB, tA, tB;
         get_supports(*A, normalized(xform_inv(xA->b, -best_axis)), sA, nA, tA);
@@ -65,12 +73,14 @@ struct Separator {
     }
 };
 
+template <bool TEST>
 __device__ inline void analytic_sphere_collision(V3 oa, float ra, V3 ob, float rb, Collector &c) {
     V3 b_to_a = oa - ob;
     float len = length(b_to_a);
     float overlap = ra + rb - len;
     if (overlap < 0) return;
     c.collided = true;
+    if (TEST) return;
     if ((double)len < BPC_CMP_EPSILON) b_to_a = V3(0.f, 1.f, 0.f);
     else b_to_a /= len;
     if (ra < rb) {
@@ -84,10 +94,12 @@ __device__ inline void analytic_sphere_collision(V3 oa, float ra, V3 ob, float r
     }
 }
 
+template <bool TEST>
 __device__ inline void col_sphere_sphere(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
-    analytic_sphere_collision(xa.o, a.p.x * length(xa.b.r[0]), xb.o, b.p.x * length(xb.b.r[0]), c);
+    analytic_sphere_collision<TEST>(xa.o, a.p.x * length(xa.b.r[0]), xb.o, b.p.x * length(xb.b.r[0]), c);
 }
 
+template <bool TEST>
 __device__ inline void col_sphere_box(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     V3 center = xform(affine_inverse(xb), xa.o);
     V3 ext(b.p.x, b.p.y, b.p.z);
@@ -98,6 +110,7 @@ __device__ inline void col_sphere_box(const Sh &a, const X3 &xa, const Sh &b, co
     float radius = a.p.x * length(xa.b.r[0]);
     if (len > radius + 0.f + 0.f) return;
     c.collided = true;
+    if (TEST) return;
     V3 axis;
     if (len == 0) axis = normalized(xb.o - nearest);
     else axis = delta / len;
@@ -105,13 +118,14 @@ __device__ inline void col_sphere_box(const Sh &a, const X3 &xa, const Sh &b, co
     c.call(pa, nearest);
 }
 
+template <bool TEST>
 __device__ inline void col_sphere_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     float scale_A = length(xa.b.r[0]);
     float scale_B = length(xb.b.r[0]);
     V3 cap_axis = xb.b.col(1) * (b.p.y * 0.5f - b.p.x);
     V3 s0 = xb.o + cap_axis, s1 = xb.o - cap_axis;
     V3 closest = closest_point_to_segment(xa.o, s0, s1);
-    analytic_sphere_collision(xa.o, a.p.x * scale_A, closest, b.p.x * scale_B, c);
+    analytic_sphere_collision<TEST>(xa.o, a.p.x * scale_A, closest, b.p.x * scale_B, c);
 }
 
 // geometry_3d.cpp:36-131 (David Eberly's segment-segment distance)
@@ -179,6 +193,7 @@ __device__ inline void closest_points_between_segments(V3 p0, V3 p1, V3 q0, V3 q
     qt = (1 - t) * q0 + t * q1;
 }
 
+template <bool TEST>
 __device__ inline void col_capsule_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     float scale_A = length(xa.b.r[0]);
     float scale_B = length(xb.b.r[0]);
@@ -186,13 +201,14 @@ __device__ inline void col_capsule_capsule(const Sh &a, const X3 &xa, const Sh &
     V3 axB = xb.b.col(1) * (b.p.y * 0.5f - b.p.x);
     V3 ca, cbp;
     closest_points_between_segments(xa.o + axA, xa.o - axA, xb.o + axB, xb.o - axB, ca, cbp);
-    analytic_sphere_collision(ca, a.p.x * scale_A, cbp, b.p.x * scale_B, c);
+    analytic_sphere_collision<TEST>(ca, a.p.x * scale_A, cbp, b.p.x * scale_B, c);
 }
 
 __device__ inline V3 box_corner_toward(const Sh &box, const X3 &xf, V3 cn) {
     return xform(xf, V3((cn.x < 0) ? -box.p.x : box.p.x, (cn.y < 0) ? -box.p.y : box.p.y, (cn.z < 0) ? -box.p.z : box.p.z));
 }
 
+template <bool TEST>
 __device__ inline void col_box_box(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     Separator sep;
     sep.init(&a, &xa, &b, &xb, &c);
@@ -211,9 +227,10 @@ __device__ inline void col_box_box(const Sh &a, const X3 &xa, const Sh &b, const
             if (!sep.test_axis(axis)) return;
         }
     }
-    sep.generate_contacts();
+    sep.template generate_contacts<TEST>();
 }
 
+template <bool TEST>
 __device__ inline void col_box_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     Separator sep;
     sep.init(&a, &xa, &b, &xb, &c);
@@ -256,9 +273,10 @@ __device__ inline void col_box_capsule(const Sh &a, const X3 &xa, const Sh &b, c
             if (!sep.test_axis(axis)) return;
         }
     }
-    sep.generate_contacts();
+    sep.template generate_contacts<TEST>();
 }
 
+template <bool TEST>
 __device__ inline void col_sphere_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     Separator sep;
     sep.init(&a, &xa, &b, &xb, &c);
@@ -278,9 +296,10 @@ __device__ inline void col_sphere_convex(const Sh &a, const X3 &xa, const Sh &b,
         V3 v1 = xform(xb, mv_vert(m, i));
         if (!sep.test_axis(normalized(xa.o - v1))) return;
     }
-    sep.generate_contacts();
+    sep.template generate_contacts<TEST>();
 }
 
+template <bool TEST>
 __device__ inline void col_box_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     Separator sep;
     sep.init(&a, &xa, &b, &xb, &c);
@@ -301,9 +320,10 @@ __device__ inline void col_box_convex(const Sh &a, const X3 &xa, const Sh &b, co
             if (!sep.test_axis(normalized(cross(e1, e2)))) return;
         }
     }
-    sep.generate_contacts();
+    sep.template generate_contacts<TEST>();
 }
 
+template <bool TEST>
 __device__ inline void col_capsule_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     Separator sep;
     sep.init(&a, &xa, &b, &xb, &c);
@@ -328,7 +348,7 @@ __device__ inline void col_capsule_convex(const Sh &a, const X3 &xa, const Sh &b
             if (!sep.test_axis(normalized(cross(cross(n1, n2), n2)))) return;
         }
     }
-    sep.generate_contacts();
+    sep.template generate_contacts<TEST>();
 }
 
 __device__ __forceinline__ bool is_minkowski_face(V3 A, V3 B, V3 B_x_A, V3 C, V3 D, V3 D_x_C) {
@@ -336,6 +356,7 @@ __device__ __forceinline__ bool is_minkowski_face(V3 A, V3 B, V3 B_x_A, V3 C, V3
     return (CBA * DBA < 0.0f) && (ADC * BDC < 0.0f) && (CBA * BDC > 0.0f);
 }
 
+template <bool TEST>
 __device__ inline void col_convex_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     Separator sep;
     sep.init(&a, &xa, &b, &xb, &c);
@@ -366,10 +387,11 @@ __device__ inline void col_convex_convex(const Sh &a, const X3 &xa, const Sh &b,
             }
         }
     }
-    sep.generate_contacts();
+    sep.template generate_contacts<TEST>();
 }
 
 // plane (world boundary, shape A of the call) against any supported shape
+template <bool TEST>
 __device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, const X3 &xb, Collector &c, bool swap_result) {
     // Transform3D::xform(Plane): transform_3d.h:154-158, 241-252
     M3 bit = transposed(inverse(xp.b));
@@ -386,6 +408,7 @@ __device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, 
         V3 s = xform(xb, sup[i]);
         if (pl_distance(p, s) >= 0) continue;
         found = true;
+        if (TEST) return true;
         V3 sa = pl_project(p, s);
         if (swap_result) manifold_add(*c.m, s, sa);
         else manifold_add(*c.m, sa, s);
@@ -394,6 +417,7 @@ __device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, 
 }
 
 // BradotCollisionSolver3D::solve_static (…collision_solver_3d.cpp:362-435) + sat_calculate_penetration dispatch (…sat.cpp:2296-2421)
+template <bool TEST>
 __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, const X3 &xb, Manifold &m, V3 *sep_axis) {
     Collector c;
     c.m = &m;
@@ -404,8 +428,8 @@ __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, co
     uint32_t ta = sa.type, tb = sb.type;
     if (min(ta, tb) == SH_PLANE) {
         if (ta == SH_PLANE && tb == SH_PLANE) return false;
-        if (ta > tb) return col_plane(sb, xb, sa, xa, c, true);
-        return col_plane(sa, xa, sb, xb, c, false);
+        if (ta > tb) return col_plane<TEST>(sb, xb, sa, xa, c, true);
+        return col_plane<TEST>(sa, xa, sb, xb, c, false);
     }
     const Sh *A = &sa, *B = &sb;
     const X3 *XA = &xa, *XB = &xb;
@@ -415,19 +439,19 @@ __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, co
         c.swap = true;
     }
     if (ta == SH_SPHERE) {
-        if (tb == SH_SPHERE) col_sphere_sphere(*A, *XA, *B, *XB, c);
-        else if (tb == SH_BOX) col_sphere_box(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CAPSULE) col_sphere_capsule(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CONVEX) col_sphere_convex(*A, *XA, *B, *XB, c);
+        if (tb == SH_SPHERE) col_sphere_sphere<TEST>(*A, *XA, *B, *XB, c);
+        else if (tb == SH_BOX) col_sphere_box<TEST>(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CAPSULE) col_sphere_capsule<TEST>(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CONVEX) col_sphere_convex<TEST>(*A, *XA, *B, *XB, c);
     } else if (ta == SH_BOX) {
-        if (tb == SH_BOX) col_box_box(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CAPSULE) col_box_capsule(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CONVEX) col_box_convex(*A, *XA, *B, *XB, c);
+        if (tb == SH_BOX) col_box_box<TEST>(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CAPSULE) col_box_capsule<TEST>(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CONVEX) col_box_convex<TEST>(*A, *XA, *B, *XB, c);
     } else if (ta == SH_CAPSULE) {
-        if (tb == SH_CAPSULE) col_capsule_capsule(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CONVEX) col_capsule_convex(*A, *XA, *B, *XB, c);
+        if (tb == SH_CAPSULE) col_capsule_capsule<TEST>(*A, *XA, *B, *XB, c);
+        else if (tb == SH_CONVEX) col_capsule_convex<TEST>(*A, *XA, *B, *XB, c);
     } else if (ta == SH_CONVEX && tb == SH_CONVEX) {
-        col_convex_convex(*A, *XA, *B, *XB, c);
+        col_convex_convex<TEST>(*A, *XA, *B, *XB, c);
     }
     return c.collided;
 }
