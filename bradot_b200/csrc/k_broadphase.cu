@@ -264,23 +264,39 @@ __global__ void __launch_bounds__(BP_THREADS) k_traverse(int n, const float4 *__
     }
 }
 
+// Run of each body (as the pair's A) in the previous, sorted pair list: the lookup of k_match then
+// searches a handful of keys instead of the whole list.
+__global__ void __launch_bounds__(BP_THREADS) k_a_ranges(uint32_t n_old, const uint64_t *__restrict__ kold, uint32_t *__restrict__ a_begin,
+                                                         uint32_t *__restrict__ a_end) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_old) return;
+    uint32_t A = (uint32_t)(kold[k] >> 32);
+    if (k == 0 || (uint32_t)(kold[k - 1] >> 32) != A) a_begin[A] = k;
+    if (k == n_old - 1 || (uint32_t)(kold[k + 1] >> 32) != A) a_end[A] = k + 1;
+}
+
 // Carry the persistent manifold across the re-sorted pair list and count pairs per item.
 __global__ void __launch_bounds__(BP_THREADS) k_match(uint32_t n_new, const uint64_t *__restrict__ knew, uint32_t n_old,
                                                       const uint64_t *__restrict__ kold, const PairHdr *__restrict__ hold,
                                                       const ContactGeo *__restrict__ gold, const ContactAcc *__restrict__ aold,
                                                       PairHdr *__restrict__ hnew, ContactGeo *__restrict__ gnew, ContactAcc *__restrict__ anew,
-                                                      uint32_t *__restrict__ npairs) {
+                                                      uint32_t *__restrict__ npairs, const uint32_t *__restrict__ a_begin,
+                                                      const uint32_t *__restrict__ a_end, const uint4 *__restrict__ meta) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n_new) return;
     uint64_t key = knew[k];
-    atomicAdd(&npairs[(uint32_t)(key >> 32)], 1u);
-    atomicAdd(&npairs[(uint32_t)key], 1u);
-    uint32_t lo = 0, hi = n_old;
+    // pair counts only steer the margin of items that move; a world boundary pairs with every body of
+    // its space, and counting those on one address would serialise the kernel
+    if ((meta[(uint32_t)(key >> 32)].x & 0xffu) != MODE_STATIC) atomicAdd(&npairs[(uint32_t)(key >> 32)], 1u);
+    if ((meta[(uint32_t)key].x & 0xffu) != MODE_STATIC) atomicAdd(&npairs[(uint32_t)key], 1u);
+    uint32_t A = (uint32_t)(key >> 32);
+    uint32_t lo = a_begin[A], hi = a_end[A], end = hi; // empty run: begin = end = 0
     while (lo < hi) {
         uint32_t mid = (lo + hi) >> 1;
         if (kold[mid] < key) lo = mid + 1;
         else hi = mid;
     }
+    if (lo >= end) lo = n_old; // not found
     PairHdr h;
     h.sep = make_float4(0.f, 0.f, 0.f, 0.f);
     if (lo < n_old && kold[lo] == key) {
@@ -390,10 +406,22 @@ int bpc_launch_broadphase(bpc_context *ctx) {
     if (bpc_radix_sort(ctx, &a, &b, nullptr, nullptr, found, lowmask | (lowmask << 32))) return -1;
     if (a != kdst && found) BPC_CHECK(cudaMemcpyAsync(kdst, a, (size_t)found * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
     BPC_CHECK(cudaMemsetAsync(ctx->npairs.p, 0, (size_t)ctx->n_bodies * sizeof(uint32_t), st));
+    ctx->a_range.reserve((size_t)ctx->n_bodies * 2, false, st);
+    if (!ctx->a_range.p) {
+        ctx->err = "broadphase: out of device memory";
+        return -1;
+    }
+    BPC_CHECK(cudaMemsetAsync(ctx->a_range.p, 0, (size_t)ctx->n_bodies * 2 * sizeof(uint32_t), st));
+    if (ctx->n_pairs[ctx->cur]) {
+        k_a_ranges<<<nblk(ctx->n_pairs[ctx->cur], BP_THREADS), BP_THREADS, 0, st>>>(ctx->n_pairs[ctx->cur], ctx->pair_keys[ctx->cur].p, ctx->a_range.p,
+                                                                                      ctx->a_range.p + ctx->n_bodies);
+        ctx->launches += 1;
+    }
     if (found) {
         k_match<<<nblk(found, BP_THREADS), BP_THREADS, 0, st>>>(found, kdst, ctx->n_pairs[ctx->cur], ctx->pair_keys[ctx->cur].p,
                                                                 ctx->pair_hdr[ctx->cur].p, ctx->cgeo[ctx->cur].p, ctx->cacc[ctx->cur].p,
-                                                                ctx->pair_hdr[nxt].p, ctx->cgeo[nxt].p, ctx->cacc[nxt].p, ctx->npairs.p);
+                                                                ctx->pair_hdr[nxt].p, ctx->cgeo[nxt].p, ctx->cacc[nxt].p, ctx->npairs.p, ctx->a_range.p,
+                                                                ctx->a_range.p + ctx->n_bodies, ctx->meta.p);
         ctx->launches += 1;
     }
     BPC_CHECK(cudaGetLastError());
