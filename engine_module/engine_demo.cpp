@@ -1,0 +1,180 @@
+// engine_demo -- proves the drop-in path end to end: brings up the engine core (the reference's own objects,
+// linked from oracle/_ref/libbradot_ref.a), registers "BradotPhysicsCUDA" with PhysicsServer3DManager, asks the
+// manager for that server BY NAME, builds a scene file through the public PhysicsServer3D RID API and steps it.
+// Body transforms after the last step go to stdout as JSON for comparison with a direct C-ABI run.
+// Host code only (no CUDA here): it reaches the GPU solely through libbradot_physics_cuda.so.
+#include "core/config/engine.h"
+#include "core/config/project_settings.h"
+#include "core/io/file_access_pack.h"
+#include "core/object/worker_thread_pool.h"
+#include "core/register_core_types.h"
+#include "drivers/unix/os_unix.h"
+#include "servers/physics_server_3d.h"
+
+#include "bradot_physics_cuda/register_types.h"
+
+#include <unistd.h>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+class OSHeadless : public OS_Unix {
+public:
+	MainLoop *ml = nullptr;
+	void initialize() override { initialize_core(); }
+	void initialize_joypads() override {}
+	void set_main_loop(MainLoop *p) override { ml = p; }
+	void delete_main_loop() override {}
+	void finalize() override {}
+	bool _check_internal_feature_support(const String &) override { return false; }
+	MainLoop *get_main_loop() const override { return ml; }
+};
+
+#pragma pack(push, 1)
+struct ScnHeader { char magic[4]; uint32_t version, n_spaces, n_shapes, n_bodies, n_joints, n_verts; float dt; uint32_t iterations, reserved[7]; };
+struct ScnShape { uint32_t type; float p[4]; uint32_t vert_ofs, vert_cnt, pad; };
+struct ScnBody { uint32_t space, mode, shape, flags; float xf[12], shape_xf[12], linvel[3], angvel[3], mass, friction, bounce, gravity_scale, lin_damp, ang_damp; uint32_t layer, mask; };
+struct ScnJoint { uint32_t type, body_a, body_b, flags; float fa[12], fb[12]; };
+#pragma pack(pop)
+
+static Transform3D xf_from(const float *f) {
+	return Transform3D(Basis(f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7], f[8]), Vector3(f[9], f[10], f[11]));
+}
+
+int main(int argc, char **argv) {
+	if (argc < 3) {
+		fprintf(stderr, "usage: engine_demo scene.bscn steps\n");
+		return 2;
+	}
+	int steps = atoi(argv[2]);
+	FILE *sf = fopen(argv[1], "rb");
+	ScnHeader hd;
+	if (!sf || fread(&hd, sizeof(hd), 1, sf) != 1 || memcmp(hd.magic, "BSCN", 4) != 0) {
+		fprintf(stderr, "bad scene file\n");
+		return 2;
+	}
+	std::vector<ScnShape> shapes(hd.n_shapes);
+	std::vector<ScnBody> bodies(hd.n_bodies);
+	std::vector<ScnJoint> joints(hd.n_joints);
+	std::vector<float> verts(hd.n_verts * 3);
+	if (hd.n_shapes && fread(shapes.data(), sizeof(ScnShape), hd.n_shapes, sf) != hd.n_shapes) return 2;
+	if (hd.n_bodies && fread(bodies.data(), sizeof(ScnBody), hd.n_bodies, sf) != hd.n_bodies) return 2;
+	if (hd.n_joints && fread(joints.data(), sizeof(ScnJoint), hd.n_joints, sf) != hd.n_joints) return 2;
+	if (hd.n_verts && fread(verts.data(), 12, hd.n_verts, sf) != hd.n_verts) return 2;
+	fclose(sf);
+
+	OSHeadless os;
+	Thread::make_main_thread();
+	set_current_thread_safe_for_nodes(true);
+	os.initialize();
+	memnew(Engine);
+	register_core_types();
+	memnew(PackedData);
+	memnew(ProjectSettings);
+	register_core_settings();
+	WorkerThreadPool::get_singleton()->init(-1, 0.3);
+
+	// what Main::setup / initialize_physics do (main/main.cpp:319-337): registry, module init, server by name
+	PhysicsServer3DManager *manager = memnew(PhysicsServer3DManager);
+	initialize_bradot_physics_cuda_module(MODULE_INITIALIZATION_LEVEL_SERVERS);
+	PhysicsServer3D *ps = manager->new_server("BradotPhysicsCUDA");
+	if (!ps) {
+		fprintf(stderr, "PhysicsServer3DManager::new_server(\"BradotPhysicsCUDA\") returned null\n");
+		return 1;
+	}
+	ps->init();
+
+	std::vector<RID> space_r, shape_r, body_r;
+	for (uint32_t i = 0; i < hd.n_spaces; i++) {
+		RID sp = ps->space_create();
+		ps->space_set_active(sp, true);
+		ps->space_set_param(sp, PhysicsServer3D::SPACE_PARAM_SOLVER_ITERATIONS, hd.iterations);
+		space_r.push_back(sp);
+	}
+	for (const ScnShape &s : shapes) {
+		RID sh;
+		switch (s.type) {
+			case PhysicsServer3D::SHAPE_WORLD_BOUNDARY:
+				sh = ps->world_boundary_shape_create();
+				ps->shape_set_data(sh, Plane(Vector3(s.p[0], s.p[1], s.p[2]), s.p[3]));
+				break;
+			case PhysicsServer3D::SHAPE_SPHERE:
+				sh = ps->sphere_shape_create();
+				ps->shape_set_data(sh, s.p[0]);
+				break;
+			case PhysicsServer3D::SHAPE_BOX:
+				sh = ps->box_shape_create();
+				ps->shape_set_data(sh, Vector3(s.p[0], s.p[1], s.p[2]));
+				break;
+			case PhysicsServer3D::SHAPE_CAPSULE: {
+				sh = ps->capsule_shape_create();
+				Dictionary d;
+				d["radius"] = s.p[0];
+				d["height"] = s.p[1];
+				ps->shape_set_data(sh, d);
+			} break;
+			case PhysicsServer3D::SHAPE_CONVEX_POLYGON: {
+				sh = ps->convex_polygon_shape_create();
+				Vector<Vector3> pts;
+				for (uint32_t k = 0; k < s.vert_cnt; k++) {
+					const float *v = &verts[(s.vert_ofs + k) * 3];
+					pts.push_back(Vector3(v[0], v[1], v[2]));
+				}
+				ps->shape_set_data(sh, pts);
+			} break;
+			default:
+				fprintf(stderr, "unsupported shape\n");
+				return 2;
+		}
+		shape_r.push_back(sh);
+	}
+	for (const ScnBody &b : bodies) {
+		RID body = ps->body_create();
+		ps->body_set_mode(body, (PhysicsServer3D::BodyMode)b.mode);
+		ps->body_add_shape(body, shape_r[b.shape], xf_from(b.shape_xf), false);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_MASS, b.mass);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_FRICTION, b.friction);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_BOUNCE, b.bounce);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_GRAVITY_SCALE, b.gravity_scale);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_LINEAR_DAMP, b.lin_damp);
+		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_ANGULAR_DAMP, b.ang_damp);
+		ps->body_set_collision_layer(body, b.layer);
+		ps->body_set_collision_mask(body, b.mask);
+		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_TRANSFORM, xf_from(b.xf));
+		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
+		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(b.angvel[0], b.angvel[1], b.angvel[2]));
+		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, (b.flags & 1) != 0);
+		ps->body_set_space(body, space_r[b.space]);
+		body_r.push_back(body);
+	}
+	ps->step(hd.dt); // uploads the bodies; joints need uploaded bodies, so they are made after the first tick here
+	for (const ScnJoint &j : joints) {
+		RID jr = ps->joint_create();
+		if (j.type == 0) {
+			ps->joint_make_pin(jr, body_r[j.body_a], Vector3(j.fa[9], j.fa[10], j.fa[11]), body_r[j.body_b], Vector3(j.fb[9], j.fb[10], j.fb[11]));
+		} else {
+			ps->joint_make_hinge(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
+		}
+		if (j.flags & 1) {
+			ps->joint_disable_collisions_between_bodies(jr, true);
+		}
+	}
+	for (int s = 1; s < steps; s++) {
+		ps->sync();
+		ps->flush_queries();
+		ps->end_sync();
+		ps->step(hd.dt);
+	}
+	ps->sync();
+	printf("{\"server\": \"BradotPhysicsCUDA\", \"steps\": %d, \"active_objects\": %d, \"collision_pairs\": %d, \"island_count\": %d, \"origins\": [",
+			steps, ps->get_process_info(PhysicsServer3D::INFO_ACTIVE_OBJECTS), ps->get_process_info(PhysicsServer3D::INFO_COLLISION_PAIRS),
+			ps->get_process_info(PhysicsServer3D::INFO_ISLAND_COUNT));
+	for (size_t i = 0; i < body_r.size(); i++) {
+		Transform3D t = ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM);
+		printf("%s[%.9g, %.9g, %.9g]", i ? ", " : "", t.origin.x, t.origin.y, t.origin.z);
+	}
+	printf("]}\n");
+	fflush(stdout);
+	ps->finish();
+	_exit(0);
+}

@@ -1,0 +1,40 @@
+"""Drop-in boundary, end to end: the engine core (reference objects) + our module, server obtained BY NAME from
+PhysicsServer3DManager, scene built through the public PhysicsServer3D RID API (engine_module/engine_demo.cpp).
+The body positions must equal a direct C-ABI run of the same scene bit for bit: same library, same kernels."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import parity
+from bradot_b200 import scenes, server
+
+pytestmark = pytest.mark.gpu
+DEMO = os.path.join(parity.ROOT, "engine_module", "_build", "engine_demo")
+
+
+def test_engine_module_matches_direct_c_abi(tmp_path):
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    sc = scenes.mixed_pile(4, half=3.0)
+    path = str(tmp_path / "scene.bscn")
+    sc.write(path)
+    steps = 80
+    r = subprocess.run([DEMO, path, str(steps)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["server"] == "BradotPhysicsCUDA"
+    engine = np.array(out["origins"], np.float32)
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc)
+    for _ in range(steps):
+        ps.step(sc.dt)
+    direct = ps.bodies_read(server.FIELD_TRANSFORM)[:, 9:12]
+    st = ps.stats()
+    ps.finish()
+    assert engine.shape == direct.shape
+    assert np.array_equal(engine, direct), float(np.abs(engine - direct).max())
+    assert out["collision_pairs"] == st["collision_pairs"] and out["active_objects"] == st["active_objects"]
+    assert st["contact_pairs"] > 0
