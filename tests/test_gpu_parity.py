@@ -128,3 +128,18 @@ def test_teacher_forced_joint_chains():     # pin + hinge chains of convex hulls
     assert w["contact"] < CONTACT_TOL, w
     assert w["state"] < STATE_TOL, w
     assert w["colliding"] > 0
+
+
+@pytest.mark.parametrize("name", ["pyramid21", "mixed27", "chains12"])
+def test_teacher_forced_from_committed_golden_dump(name):
+    """Same comparison as above, against the committed fixtures (outputs of the reference, tests/golden/):
+    runs even where the oracle binary is not available."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(parity.ROOT, "tests", "golden"))
+    import make_golden
+    make, steps, first = make_golden.FIXTURES[name]
+    dump = scenes.read_dump(os.path.join(parity.GOLDEN, name + ".bdmp"))
+    w = parity.teacher_forced(make(), steps, list(range(first, steps)), dump=dump)
+    assert w["contact"] < CONTACT_TOL and w["state"] < STATE_TOL, w
+    assert w["colliding"] > 0
