@@ -12,7 +12,11 @@
 namespace cg = cooperative_groups;
 
 #define SV_THREADS 128
-#define MIN_VELOCITY 0.0001 // double in the reference (bradot_body_pair_3d.cpp:39)
+// MIN_VELOCITY 0.0001 and CMP_EPSILON 0.00001 are doubles in the reference (bradot_body_pair_3d.cpp:39, math_defs.h:35) and
+// the floats are promoted for the compare.  float(0.0001) < 0.0001 < nextafter(float(0.0001)), so for a float x
+// "(double)x > 0.0001" is exactly "x > 0.0001f" (same for 0.00001): the compares stay in fp32, bit-identical.
+#define MIN_VELOCITY_F 0.0001f
+#define CMP_EPSILON_F 0.00001f
 
 struct SvArgs {
     uint32_t n_pairs;
@@ -161,6 +165,8 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
 
 __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
     uint4 inf = a.info[s];
+    // first contact record requested together with the info word: its latency overlaps the body gathers
+    SolveContact first = a.sc[(size_t)s * 4];
     if (!(inf.z & 0x800u)) return;
     uint32_t ia = inf.x, ib = inf.y;
     int count = inf.z & 0xffu;
@@ -171,7 +177,7 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
     load_body(a, ib, cB, B, f2, f3);
     bool touched = false;
     for (int c = 0; c < count; c++) {
-        SolveContact sc = a.sc[(size_t)s * 4 + c];
+        SolveContact sc = c == 0 ? first : a.sc[(size_t)s * 4 + c];
         if (sc.b.w == 0.f) continue;
         bool active = false;
         V3 n = f4v(sc.n_mn), rA = f4v(sc.ra_b), rB = f4v(sc.rb_bo);
@@ -180,7 +186,7 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
         V3 crbA = cross(A.bang, rA), crbB = cross(B.bang, rB);
         V3 dbv = B.blin + crbB - A.blin - crbA;
         float vbn = dot(dbv, n);
-        if ((double)fabsf(-vbn + cbias) > MIN_VELOCITY) {
+        if (fabsf(-vbn + cbias) > MIN_VELOCITY_F) {
             float jbn = (-vbn + cbias) * mass_normal;
             float jbnOld = sc.b.x;
             sc.b.x = fmaxf(jbnOld + jbn, 0.0f);
@@ -191,7 +197,7 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
             crbB = cross(B.bang, rB);
             dbv = B.blin + crbB - A.blin - crbA;
             vbn = dot(dbv, n);
-            if ((double)fabsf(-vbn + cbias) > MIN_VELOCITY) {
+            if (fabsf(-vbn + cbias) > MIN_VELOCITY_F) {
                 float jbn_com = (-vbn + cbias) / (A.inv_mass + B.inv_mass);
                 float old = sc.b.y;
                 sc.b.y = fmaxf(old + jbn_com, 0.0f);
@@ -205,7 +211,7 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
         V3 crA = cross(A.ang, rA), crB = cross(B.ang, rB);
         V3 dv = B.lin + crB - A.lin - crA;
         float vn = dot(dv, n);
-        if ((double)fabsf(vn) > MIN_VELOCITY) {
+        if (fabsf(vn) > MIN_VELOCITY_F) {
             float jn = -(bounce + vn) * mass_normal;
             float jnOld = sc.t_n.w;
             sc.t_n.w = fmaxf(jnOld + jn, 0.0f);
@@ -222,7 +228,7 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
         float tn = dot(n, dtv);
         V3 tv = dtv - n * tn;
         float tvl = length(tv);
-        if ((double)tvl > MIN_VELOCITY) {
+        if (tvl > MIN_VELOCITY_F) {
             tv /= tvl;
             V3 temp1 = xform(A.iinv, cross(rA, tv));
             V3 temp2 = xform(B.iinv, cross(rB, tv));
@@ -232,7 +238,7 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
             V3 acc_t = jtOld + jt;
             float fi_len = length(acc_t);
             float jtMax = sc.t_n.w * friction;
-            if ((double)fi_len > BPC_CMP_EPSILON && fi_len > jtMax) acc_t *= jtMax / fi_len;
+            if (fi_len > CMP_EPSILON_F && fi_len > jtMax) acc_t *= jtMax / fi_len;
             jt = acc_t - jtOld;
             if (cA) apply_impulse(A, -jt, rA + A.com);
             if (cB) apply_impulse(B, jt, rB + B.com);
