@@ -145,10 +145,23 @@ static bool grow(bpc_context *ctx, DevBuf<T> &b, size_t n) {
 
 static int rebuild_item_lists(bpc_context *ctx) {
     std::vector<uint32_t> tree, big;
+    uint32_t nsp = (uint32_t)ctx->spaces.size();
+    std::vector<uint32_t> start(nsp + 1, 0);
     for (uint32_t i = 0; i < ctx->n_bodies; i++) {
-        if (ctx->h_big[i]) big.push_back(i);
+        if (ctx->h_big[i]) start[ctx->h_space_of[i] + 1]++;
         else tree.push_back(i);
     }
+    for (uint32_t s = 0; s < nsp; s++) start[s + 1] += start[s];
+    big.resize(start[nsp]);
+    {
+        std::vector<uint32_t> cur(start.begin(), start.end() - 1);
+        for (uint32_t i = 0; i < ctx->n_bodies; i++) {
+            if (ctx->h_big[i]) big[cur[ctx->h_space_of[i]]++] = i;
+        }
+    }
+    ctx->big_start.reserve(nsp + 1, false, ctx->stream);
+    if (!ctx->big_start.p) return fail(ctx, "out of device memory");
+    BPC_CHECK(cudaMemcpyAsync(ctx->big_start.p, start.data(), (nsp + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
     ctx->tree_items.reserve(tree.size() + 1, false, ctx->stream);
     ctx->big_items.reserve(big.size() + 1, false, ctx->stream);
     if (!ctx->tree_items.p || !ctx->big_items.p) return fail(ctx, "out of device memory");
@@ -186,6 +199,7 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
     std::vector<float4> sp(n);
     ctx->h_mode.resize(total);
     ctx->h_big.resize(total);
+    ctx->h_space_of.resize(total);
     for (int i = 0; i < n; i++) {
         const bpc_body_desc &d = descs[i];
         const ShapeRec &sh = ctx->h_shapes[d.shape];
@@ -210,6 +224,7 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
         if (sh.meta.x == SH_CONVEX) memcpy(&sp[i].x, &sh.meta.y, 4);
         sid[i] = d.shape;
         ctx->h_mode[first + i] = (uint8_t)d.mode;
+        ctx->h_space_of[first + i] = d.space;
         ctx->h_big[first + i] = (d.mode == MODE_STATIC && sh.meta.x == SH_PLANE) ? 1 : 0;
     }
     cudaStream_t st = ctx->stream;

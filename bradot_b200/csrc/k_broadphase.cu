@@ -203,7 +203,7 @@ __device__ __forceinline__ void emit_pair(uint64_t key, uint64_t *__restrict__ o
 
 __global__ void __launch_bounds__(BP_THREADS) k_traverse(int n, const float4 *__restrict__ leaf_min, const float4 *__restrict__ leaf_max,
                                                          const float4 *__restrict__ nodes, const uint4 *__restrict__ meta,
-                                                         const ItemBox *__restrict__ items, const uint32_t *__restrict__ big, uint32_t n_big,
+                                                         const ItemBox *__restrict__ items, const uint32_t *__restrict__ big, const uint32_t *__restrict__ big_start,
                                                          uint64_t *__restrict__ out, uint32_t cap, uint32_t *__restrict__ counter) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -213,10 +213,9 @@ __global__ void __launch_bounds__(BP_THREADS) k_traverse(int n, const float4 *__
     if ((qm.x & 0xffu) == MODE_STATIC) return; // the static tree never queries (tree masks, bradot_broad_phase_3d_bvh.cpp:37-38)
     uint32_t qsp = qm.w;
     // unbounded statics (world boundaries): brute force
-    for (uint32_t k = 0; k < n_big; k++) {
+    for (uint32_t k = big_start[qsp], ke = big_start[qsp + 1]; k < ke; k++) {
         uint32_t j = big[k];
         uint4 jm = meta[j];
-        if (jm.w != qsp) continue;
         if (!((qm.y & jm.z) || (jm.y & qm.z))) continue; // interacts_with, bradot_collision_object_3d.h:181-183
         ItemBox jb = items[j];
         if (!boxes_overlap(qmin, qmax, jb.smin, jb.smax)) continue;
@@ -384,7 +383,7 @@ int bpc_launch_broadphase(bpc_context *ctx) {
         BPC_CHECK(cudaMemsetAsync(ctx->counters.p + CNT_PAIRS, 0, sizeof(uint32_t), st));
         if (n) {
             k_traverse<<<nblk(n, BP_THREADS), BP_THREADS, 0, st>>>((int)n, ctx->leaf_min.p, ctx->leaf_max.p, ctx->nodes.p, ctx->meta.p,
-                                                                   ctx->items.p, ctx->big_items.p, ctx->n_big, ctx->pair_keys_raw.p,
+                                                                   ctx->items.p, ctx->big_items.p, ctx->big_start.p, ctx->pair_keys_raw.p,
                                                                    (uint32_t)ctx->pair_cap, ctx->counters.p + CNT_PAIRS);
             ctx->launches += 1;
         }

@@ -296,15 +296,26 @@ def convex_chains(n_chains=25000, chain_len=8, n_hulls=64, seed=11):
 
 # ------------------------------------------------------------------------ C5
 def batched_worlds(n_spaces=4096, seed0=1000, lattice=(8, 4, 8)):
-    """C5: independent spaces, each a plane + a small mixed pile."""
+    """C5: independent spaces, each a plane + a small mixed pile (seed0 + space index per space).
+    Records are collected per space and concatenated once, so 4096 spaces build in seconds."""
     sc = Scene(n_spaces=n_spaces, name="C5_worlds_%dx%d" % (n_spaces, lattice[0] * lattice[1] * lattice[2]))
     g = np.stack(np.meshgrid(np.arange(lattice[0]), np.arange(lattice[1]), np.arange(lattice[2]), indexing="ij"),
                  -1).reshape(-1, 3)
     pos = np.stack([(g[:, 0] - (lattice[0] - 1) * 0.5) * 1.1, 1.0 + g[:, 1] * 1.1,
                     (g[:, 2] - (lattice[2] - 1) * 0.5) * 1.1], -1)
+    shape_parts, body_parts = [], []
+    n_shapes = 0
     for s in range(n_spaces):
-        sc.add_static_plane((0, 1, 0), 0.0, space=s)
-        _mixed_bodies(sc, np.random.default_rng(seed0 + s), pos, space=s)
+        tmp = Scene()
+        tmp.add_static_plane((0, 1, 0), 0.0)
+        _mixed_bodies(tmp, np.random.default_rng(seed0 + s), pos)
+        tmp.bodies["space"] = s
+        tmp.bodies["shape"] += n_shapes
+        n_shapes += len(tmp.shapes)
+        shape_parts.append(tmp.shapes)
+        body_parts.append(tmp.bodies)
+    sc.shapes = np.concatenate(shape_parts)
+    sc.bodies = np.concatenate(body_parts)
     return sc
 
 
