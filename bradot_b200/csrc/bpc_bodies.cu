@@ -274,6 +274,34 @@ extern "C" int bpc_joints_create(bpc_context *ctx, const bpc_joint_desc *descs, 
 }
 
 // ---------------------------------------------------------------------------------------------- bulk state I/O
+// The per-tick paths of an engine (read every transform / velocity, write the force accumulators) repack on the
+// device, so the only host work is one memcpy of the packed floats.
+__global__ void k_pack_xf(uint32_t n, const BodyXf *__restrict__ xf, float *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    BodyXf x = xf[i];
+    float *o = out + (size_t)i * 12;
+    o[0] = x.r0.x; o[1] = x.r0.y; o[2] = x.r0.z; o[3] = x.r1.x; o[4] = x.r1.y; o[5] = x.r1.z;
+    o[6] = x.r2.x; o[7] = x.r2.y; o[8] = x.r2.z; o[9] = x.o.x; o[10] = x.o.y; o[11] = x.o.z;
+}
+__global__ void k_pack_vel(uint32_t n, const BodyVel *__restrict__ vel, int angular, float *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = angular ? vel[i].ang : vel[i].lin;
+    out[(size_t)i * 3] = v.x; out[(size_t)i * 3 + 1] = v.y; out[(size_t)i * 3 + 2] = v.z;
+}
+__global__ void k_unpack_forces(uint32_t n, const float *__restrict__ in, BodyForces *__restrict__ forces) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *o = in + (size_t)i * 6;
+    forces[i].force = make_float4(o[0], o[1], o[2], 0.f);
+    forces[i].torque = make_float4(o[3], o[4], o[5], 0.f);
+}
+static int staging_for(bpc_context *ctx, size_t floats) {
+    ctx->staging.reserve(floats, false, ctx->stream);
+    if (!ctx->staging.p) return fail(ctx, "out of device memory");
+    return 0;
+}
 static int field_width(int field) {
     switch (field) {
         case BPC_FIELD_TRANSFORM: return 12;
@@ -308,22 +336,17 @@ extern "C" int bpc_bodies_read(bpc_context *ctx, int field, int first, int n, fl
     BPC_CHECK(cudaSetDevice(ctx->device));
     switch (field) {
         case BPC_FIELD_TRANSFORM: {
-            std::vector<BodyXf> h;
-            if (fetch(ctx, h, ctx->xf, first, n)) return -1;
-            for (int i = 0; i < n; i++) {
-                float *o = out + 12 * i;
-                o[0] = h[i].r0.x; o[1] = h[i].r0.y; o[2] = h[i].r0.z; o[3] = h[i].r1.x; o[4] = h[i].r1.y; o[5] = h[i].r1.z;
-                o[6] = h[i].r2.x; o[7] = h[i].r2.y; o[8] = h[i].r2.z; o[9] = h[i].o.x; o[10] = h[i].o.y; o[11] = h[i].o.z;
-            }
+            if (staging_for(ctx, (size_t)n * 12)) return -1;
+            k_pack_xf<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->xf.p + first, ctx->staging.p);
+            BPC_CHECK(cudaMemcpyAsync(out, ctx->staging.p, (size_t)n * 12 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+            BPC_CHECK(cudaStreamSynchronize(ctx->stream));
         } break;
         case BPC_FIELD_LINEAR_VELOCITY:
         case BPC_FIELD_ANGULAR_VELOCITY: {
-            std::vector<BodyVel> h;
-            if (fetch(ctx, h, ctx->vel, first, n)) return -1;
-            for (int i = 0; i < n; i++) {
-                float4 v = field == BPC_FIELD_LINEAR_VELOCITY ? h[i].lin : h[i].ang;
-                out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
-            }
+            if (staging_for(ctx, (size_t)n * 3)) return -1;
+            k_pack_vel<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->vel.p + first, field == BPC_FIELD_ANGULAR_VELOCITY, ctx->staging.p);
+            BPC_CHECK(cudaMemcpyAsync(out, ctx->staging.p, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+            BPC_CHECK(cudaStreamSynchronize(ctx->stream));
         } break;
         case BPC_FIELD_ACTIVE: {
             std::vector<uint4> h;
@@ -443,14 +466,10 @@ extern "C" int bpc_bodies_write(bpc_context *ctx, int field, int first, int n, c
             if (store(ctx, h, ctx->items, first) || store(ctx, np, ctx->npairs, first)) return -1;
         } break;
         case BPC_FIELD_APPLIED_FORCE: {
-            std::vector<BodyForces> h;
-            if (fetch(ctx, h, ctx->forces, first, n)) return -1;
-            for (int i = 0; i < n; i++) {
-                const float *o = in + 6 * i;
-                h[i].force = make_float4(o[0], o[1], o[2], 0.f);
-                h[i].torque = make_float4(o[3], o[4], o[5], 0.f);
-            }
-            if (store(ctx, h, ctx->forces, first)) return -1;
+            if (staging_for(ctx, (size_t)n * 6)) return -1;
+            BPC_CHECK(cudaMemcpyAsync(ctx->staging.p, in, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+            k_unpack_forces<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->staging.p, ctx->forces.p + first);
+            BPC_CHECK(cudaStreamSynchronize(ctx->stream)); // the caller may reuse its buffer right away
         } break;
     }
     if (refresh) {

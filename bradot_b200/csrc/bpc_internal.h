@@ -147,6 +147,7 @@ struct bpc_context {
     DevBuf<JointRec> d_joints;
     DevBuf<JointSetup> jsetup;
     DevBuf<uint32_t> a_range; // [2 * n_bodies]: begin / end of each body's run (as A) in the previous pair list
+    DevBuf<float> staging;    // packed per-body floats on their way to / from the host (bulk state I/O)
     DevBuf<uint32_t> np_work; // broadphase pairs that need the full narrowphase pass this step
     DevBuf<uint64_t> forced_keys;
 

@@ -168,9 +168,12 @@ class PhysicsServerCUDA:
     def body_count(self):
         return self._check(self.lib.bpc_body_count(self.ctx))
 
-    def bodies_read(self, field, first=0, n=None):
+    def bodies_read(self, field, first=0, n=None, out=None):
+        """Read `n` bodies' `field`; `out` may be a caller-owned float32 array (e.g. pinned host memory)."""
         n = self.body_count() - first if n is None else n
-        out = np.zeros((n, _FIELD_WIDTH[field]), np.float32)
+        if out is None:
+            out = np.zeros((n, _FIELD_WIDTH[field]), np.float32)
+        assert out.dtype == np.float32 and out.size == n * _FIELD_WIDTH[field] and out.flags["C_CONTIGUOUS"]
         self._check(self.lib.bpc_bodies_read(self.ctx, field, first, n, _ptr(out)))
         return out
 
