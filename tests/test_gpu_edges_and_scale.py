@@ -1,0 +1,142 @@
+"""Edge cases of the C ABI and size-independent properties at BASELINE.json's full sizes.
+
+The reference has no physics tests to mirror; these cover what its server guards with
+ERR_FAIL_* (invalid handles return an error, nothing crashes), degenerate inputs (empty context, a single
+body, bodies added between steps) and, at the 100 000-body size of the headline configuration, properties
+that do not need the oracle: the pair list is sorted / unique / complete against a brute-force overlap
+check of the stored boxes, manifolds are well formed, the run is bit-reproducible.
+"""
+import numpy as np
+import pytest
+
+from bradot_b200 import scenes, server
+
+pytestmark = pytest.mark.gpu
+
+
+def test_empty_context_and_single_body():
+    ps = server.PhysicsServerCUDA(0)
+    ps.step(1 / 60)                                  # no spaces, no bodies: a no-op, not an error
+    assert ps.stats()["collision_pairs"] == 0
+    sp = ps.space_create()
+    sh = ps.sphere_shape_create(0.5)
+    rec = np.zeros(1, scenes.BODY_DT)
+    rec["xf"] = scenes.IDENT12
+    rec["shape_xf"] = scenes.IDENT12
+    rec["mode"], rec["shape"], rec["space"], rec["mass"], rec["flags"] = scenes.MODE_RIGID, sh, sp, 2.0, 1
+    rec["gravity_scale"], rec["layer"], rec["mask"] = 1.0, 1, 1
+    ps.bodies_create(rec)
+    for _ in range(10):
+        ps.step(1 / 60)
+    v = ps.bodies_read(server.FIELD_LINEAR_VELOCITY)[0]
+    assert v[1] < -1.5 and v[0] == 0 and v[2] == 0   # ten steps of gravity with 0.1 damping
+    assert ps.stats()["active_objects"] == 1 and ps.stats()["collision_pairs"] == 0
+    ps.finish()
+
+
+def test_invalid_arguments_are_refused_not_fatal():
+    ps = server.PhysicsServerCUDA(0)
+    sp = ps.space_create()
+    sh = ps.box_shape_create((0.5, 0.5, 0.5))
+    rec = np.zeros(1, scenes.BODY_DT)
+    rec["xf"] = scenes.IDENT12
+    rec["shape_xf"] = scenes.IDENT12
+    rec["mass"], rec["mode"], rec["shape"], rec["space"] = 1.0, scenes.MODE_RIGID, sh, sp
+    for field, bad in (("space", 7), ("shape", 99), ("mode", 9), ("mode", scenes.MODE_KINEMATIC)):
+        r = rec.copy()
+        r[field] = bad
+        with pytest.raises(server.PhysicsError):
+            ps.bodies_create(r)
+    with pytest.raises(server.PhysicsError):
+        ps.shape_create(scenes.SHAPE_CYLINDER, (0.5, 1.0))      # cylinders are a "next" row: refused, never ignored
+    with pytest.raises(server.PhysicsError):
+        ps.space_set_param(3, server.SPACE_PARAM_SOLVER_ITERATIONS, 8)
+    with pytest.raises(server.PhysicsError):
+        ps.bodies_read(server.FIELD_TRANSFORM, 0, 5)            # no bodies yet
+    with pytest.raises(server.PhysicsError):
+        ps.step(0.0)
+    ps.bodies_create(rec)                                       # the context is still usable
+    ps.step(1 / 60)
+    assert ps.body_count() == 1
+    ps.finish()
+
+
+def test_bodies_added_between_steps_keep_existing_state():
+    sc = scenes.spheres_container(4, 4, 4, half=1.5)
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc)
+    for _ in range(40):
+        ps.step(sc.dt)
+    before = ps.bodies_read(server.FIELD_TRANSFORM)
+    extra = sc.bodies[5:6].copy()
+    extra["xf"][0, 9:12] = (0.0, 6.0, 0.0)
+    first = ps.bodies_create(extra)
+    assert first == len(sc.bodies)
+    assert np.array_equal(ps.bodies_read(server.FIELD_TRANSFORM, 0, first), before)
+    for _ in range(120):
+        ps.step(sc.dt)
+    y = ps.bodies_read(server.FIELD_TRANSFORM)[first, 10]
+    assert 0.2 < y < 3.0, y                                     # it fell onto the pile and stayed in the container
+    ps.finish()
+
+
+def test_sort_edge_sizes():
+    ps = server.PhysicsServerCUDA(0)
+    rng = np.random.default_rng(5)
+    for n in (0, 1, 2, 255, 256, 257, 2047, 2048, 2049, 70001):
+        k = rng.integers(0, 2 ** 63, n, dtype=np.uint64)
+        assert np.array_equal(ps.sort_u64(k), np.sort(k)), n
+    ps.finish()
+
+
+def _run_c2(steps):
+    sc = scenes.spheres_container(50, 40, 50)                    # BASELINE.json configs[1]: 100 000 spheres
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc)
+    for _ in range(steps):
+        ps.step(sc.dt)
+    return sc, ps
+
+
+def test_full_size_c2_pair_list_and_manifold_properties():
+    sc, ps = _run_c2(69)
+    boxes = ps.bodies_read(server.FIELD_ITEM_BOX)                # stored boxes the next step will pair on
+    ps.step(sc.dt)
+    ids, pf, cf = ps.pairs_read()
+    st = ps.stats()
+    keys = ids[:, 0].astype(np.int64) << 32 | ids[:, 1].astype(np.int64)
+    assert len(keys) == st["collision_pairs"] > 100000
+    assert np.all(ids[:, 0] < ids[:, 1]) and np.all(np.diff(keys) > 0)          # A < B, sorted, unique
+    # completeness and exactness against brute force on a sample of bodies
+    mn, mx = boxes[:, 6:9], boxes[:, 9:12]
+    static = sc.bodies["mode"] == scenes.MODE_STATIC
+    rng = np.random.default_rng(0)
+    key_set = set(keys.tolist())
+    for a in rng.choice(np.nonzero(~static)[0], 150, replace=False):
+        ov = np.all(mn[a] <= mx, axis=1) & np.all(mn <= mx[a], axis=1)
+        ov[a] = False
+        want = {(min(a, b) << 32) | max(a, b) for b in np.nonzero(ov)[0]}
+        got = {k for k in key_set if (k >> 32) == a or (k & 0xffffffff) == a}
+        assert got == want, (a, len(got), len(want))
+    # manifolds: colliding pairs hold 1..4 contacts with unit normals and finite, non-negative accumulated normal impulses
+    col = (ids[:, 3] & 1) > 0
+    assert st["contact_pairs"] == int(col.sum()) > 1000
+    assert np.all(ids[col, 2] >= 1) and np.all(ids[:, 2] <= 4)
+    valid = np.arange(4)[None, :] < ids[:, 2][:, None]
+    n = cf[:, :, 6:9][valid]
+    assert np.allclose(np.linalg.norm(n, axis=1), 1.0, atol=1e-5)
+    assert np.all(np.isfinite(cf)) and np.all(cf[:, :, 9][valid] >= 0)
+    xf = ps.bodies_read(server.FIELD_TRANSFORM)
+    dyn = ~static
+    assert np.all(np.isfinite(xf)) and np.all(xf[dyn, 10] > 0.0) and np.all(np.abs(xf[dyn, 9]) < 15.6) and np.all(np.abs(xf[dyn, 11]) < 15.6)
+    ps.finish()
+
+
+def test_full_size_c2_is_bit_reproducible():
+    _, a = _run_c2(50)
+    xa, va = a.bodies_read(server.FIELD_TRANSFORM), a.bodies_read(server.FIELD_LINEAR_VELOCITY)
+    a.finish()
+    _, b = _run_c2(50)
+    xb, vb = b.bodies_read(server.FIELD_TRANSFORM), b.bodies_read(server.FIELD_LINEAR_VELOCITY)
+    b.finish()
+    assert np.array_equal(xa, xb) and np.array_equal(va, vb)
