@@ -146,6 +146,7 @@ struct bpc_context {
     uint32_t stage_steps = 0;
     DevBuf<JointRec> d_joints;
     DevBuf<JointSetup> jsetup;
+    DevBuf<uint32_t> a_range_cur; // same for the current pair list (vertex-centric island pass)
     DevBuf<uint32_t> a_range; // [2 * n_bodies]: begin / end of each body's run (as A) in the previous pair list
     DevBuf<float> staging;    // packed per-body floats on their way to / from the host (bulk state I/O)
     DevBuf<uint32_t> np_work; // broadphase pairs that need the full narrowphase pass this step

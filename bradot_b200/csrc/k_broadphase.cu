@@ -423,6 +423,17 @@ int bpc_launch_broadphase(bpc_context *ctx) {
                                                                 ctx->a_range.p + ctx->n_bodies, ctx->meta.p);
         ctx->launches += 1;
     }
+    // runs of the new list, for the vertex-centric island pass
+    ctx->a_range_cur.reserve((size_t)ctx->n_bodies * 2, false, st);
+    if (!ctx->a_range_cur.p) {
+        ctx->err = "broadphase: out of device memory";
+        return -1;
+    }
+    BPC_CHECK(cudaMemsetAsync(ctx->a_range_cur.p, 0, (size_t)ctx->n_bodies * 2 * sizeof(uint32_t), st));
+    if (found) {
+        k_a_ranges<<<nblk(found, BP_THREADS), BP_THREADS, 0, st>>>(found, kdst, ctx->a_range_cur.p, ctx->a_range_cur.p + ctx->n_bodies);
+        ctx->launches += 1;
+    }
     BPC_CHECK(cudaGetLastError());
     ctx->n_pairs[nxt] = found;
     ctx->cur = nxt;

@@ -57,6 +57,22 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_union_pairs(uint32_t n_pairs,
     cc_union(label, a, b);
 }
 
+// Vertex-centric variant: one thread per body walks its run of pairs (it is the A of all of them).  Threads of a
+// warp then hook DIFFERENT trees, where the edge-parallel kernel had 32 lanes fighting over one body's root.
+__global__ void __launch_bounds__(GR_THREADS) k_cc_union_runs(uint32_t n, const uint64_t *__restrict__ keys, const uint32_t *__restrict__ a_begin,
+                                                             const uint32_t *__restrict__ a_end, const uint4 *__restrict__ meta,
+                                                             uint32_t *__restrict__ label) {
+    uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= n) return;
+    uint32_t k = a_begin[a], ke = a_end[a];
+    if (k >= ke || (meta[a].x & 0xffu) == MODE_STATIC) return;
+    for (; k < ke; k++) {
+        uint32_t b = (uint32_t)keys[k];
+        if ((meta[b].x & 0xffu) == MODE_STATIC) continue;
+        cc_union(label, a, b);
+    }
+}
+
 __global__ void __launch_bounds__(GR_THREADS) k_cc_union_joints(uint32_t n, const JointRec *__restrict__ joints, const uint4 *__restrict__ meta,
                                                                uint32_t *__restrict__ label) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -112,7 +128,12 @@ int bpc_launch_islands(bpc_context *ctx) {
     if (!n) return 0;
     cudaStream_t st = ctx->stream;
     k_cc_init<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->island_flag.p);
-    if (np) k_cc_union_pairs<<<nblk(np, GR_THREADS), GR_THREADS, 0, st>>>(np, ctx->pair_keys[ctx->cur].p, ctx->meta.p, ctx->island.p);
+    if (np && ctx->a_range_cur.p) {
+        k_cc_union_runs<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->pair_keys[ctx->cur].p, ctx->a_range_cur.p, ctx->a_range_cur.p + n,
+                                                                      ctx->meta.p, ctx->island.p);
+    } else if (np) {
+        k_cc_union_pairs<<<nblk(np, GR_THREADS), GR_THREADS, 0, st>>>(np, ctx->pair_keys[ctx->cur].p, ctx->meta.p, ctx->island.p);
+    }
     uint32_t nj = (uint32_t)ctx->h_joints.size();
     if (nj) k_cc_union_joints<<<nblk(nj, GR_THREADS), GR_THREADS, 0, st>>>(nj, ctx->d_joints.p, ctx->meta.p, ctx->island.p);
     k_cc_flatten<<<nblk(n, GR_THREADS), GR_THREADS, 0, st>>>(n, ctx->island.p, ctx->meta.p, ctx->island_flag.p);
@@ -171,7 +192,7 @@ __device__ __forceinline__ void con_bodies(uint32_t id, uint32_t n_pairs, const 
     }
 }
 
-__global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t n_joints, const uint64_t *__restrict__ keys,
+__global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t n_joints, uint32_t n_bodies, const uint64_t *__restrict__ keys,
                                                       const PairHdr *__restrict__ hdr, const JointRec *__restrict__ joints,
                                                       const uint4 *__restrict__ meta, uint32_t *__restrict__ list,
                                                       uint32_t *__restrict__ color, unsigned long long *__restrict__ best,
@@ -184,23 +205,29 @@ __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t
     uint32_t n = n_col + n_joints;
     for (uint32_t s = tid; s < n; s += nth) color[s] = 0xffffffffu;
     grid.sync();
+    // Tickets of round r live in best[r & 1]; a loser of round r bids for round r + 1 in the other array during
+    // the same pass, so a round costs one pass and one grid barrier.  A ticket carries its round in the high
+    // word, so entries left from two rounds ago can never equal (or beat) a current ticket.
+    unsigned long long *bestv[2] = { best, best + n_bodies };
+    for (uint32_t s = tid; s < n; s += nth) {
+        uint32_t id = list[s], a, b;
+        con_bodies(id, n_pairs, keys, hdr, joints, meta, a, b);
+        unsigned long long ticket = (1ull << 32) | hash32(id);
+        if (a != 0xffffffffu) atomicMax(&bestv[1][a], ticket);
+        if (b != 0xffffffffu) atomicMax(&bestv[1][b], ticket);
+    }
+    grid.sync();
     for (uint32_t round = 1; round < 4096; round++) {
-        for (uint32_t s = tid; s < n; s += nth) {
-            if (color[s] != 0xffffffffu) continue;
-            uint32_t id = list[s], a, b;
-            con_bodies(id, n_pairs, keys, hdr, joints, meta, a, b);
-            unsigned long long ticket = ((unsigned long long)round << 32) | hash32(id);
-            if (a != 0xffffffffu) atomicMax(&best[a], ticket);
-            if (b != 0xffffffffu) atomicMax(&best[b], ticket);
-        }
-        grid.sync();
+        const unsigned long long *cur = bestv[round & 1];
+        unsigned long long *nxt = bestv[(round + 1) & 1];
         uint32_t left = 0;
         for (uint32_t s = tid; s < n; s += nth) {
             if (color[s] != 0xffffffffu) continue;
             uint32_t id = list[s], a, b;
             con_bodies(id, n_pairs, keys, hdr, joints, meta, a, b);
-            unsigned long long ticket = ((unsigned long long)round << 32) | hash32(id);
-            bool win = (a == 0xffffffffu || best[a] == ticket) && (b == 0xffffffffu || best[b] == ticket);
+            uint32_t hsh = hash32(id);
+            unsigned long long ticket = ((unsigned long long)round << 32) | hsh;
+            bool win = (a == 0xffffffffu || cur[a] == ticket) && (b == 0xffffffffu || cur[b] == ticket);
             if (win) {
                 unsigned long long used = (a != 0xffffffffu ? colmask[a] : 0ull) | (b != 0xffffffffu ? colmask[b] : 0ull);
                 uint32_t c = (used == ~0ull) ? MAX_COLORS : (uint32_t)(__ffsll((long long)~used) - 1);
@@ -210,6 +237,9 @@ __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t
                     if (b != 0xffffffffu) colmask[b] |= 1ull << c;
                 }
             } else {
+                unsigned long long t2 = ((unsigned long long)(round + 1) << 32) | hsh;
+                if (a != 0xffffffffu) atomicMax(&nxt[a], t2);
+                if (b != 0xffffffffu) atomicMax(&nxt[b], t2);
                 left++;
             }
         }
@@ -279,12 +309,12 @@ int bpc_launch_schedule(bpc_context *ctx) {
     ctx->con_list.reserve(maxc, false, st);
     ctx->con_color.reserve(maxc, false, st);
     ctx->con_sorted.reserve(maxc, false, st);
-    ctx->body_best.reserve(n, false, st);
+    ctx->body_best.reserve((size_t)n * 2, false, st);
     ctx->body_colmask.reserve(n, false, st);
     ctx->color_start.reserve(2 * (MAX_COLORS + 4), false, st);
     if (np) k_con_collect<<<nblk(np, GR_THREADS), GR_THREADS, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->pair_keys[ctx->cur].p, ctx->meta.p,
                                                                         ctx->island.p, ctx->island_flag.p, ctx->con_list.p, ctx->counters.p);
-    BPC_CHECK(cudaMemsetAsync(ctx->body_best.p, 0, (size_t)n * 8, st));
+    BPC_CHECK(cudaMemsetAsync(ctx->body_best.p, 0, (size_t)n * 16, st));
     BPC_CHECK(cudaMemsetAsync(ctx->body_colmask.p, 0, (size_t)n * 8, st));
     BPC_CHECK(cudaMemsetAsync(ctx->color_start.p, 0, 2 * (MAX_COLORS + 4) * sizeof(uint32_t), st));
     BPC_CHECK(cudaMemsetAsync(ctx->counters.p + CNT_ROUND, 0, 2 * sizeof(uint32_t), st));
@@ -300,7 +330,7 @@ int bpc_launch_schedule(bpc_context *ctx) {
         const uint4 *meta = ctx->meta.p;
         uint32_t *list = ctx->con_list.p, *color = ctx->con_color.p, *counters = ctx->counters.p;
         unsigned long long *best = (unsigned long long *)ctx->body_best.p, *colmask = (unsigned long long *)ctx->body_colmask.p;
-        void *args[] = { &np, &nj, &keys, &hdr, &joints, &meta, &list, &color, &best, &colmask, &counters };
+        void *args[] = { &np, &nj, &n, &keys, &hdr, &joints, &meta, &list, &color, &best, &colmask, &counters };
         BPC_CHECK(cudaLaunchCooperativeKernel((void *)k_color, grid, block, args, 0, st));
     }
     uint32_t *start = ctx->color_start.p, *cursor = ctx->color_start.p + (MAX_COLORS + 4);
