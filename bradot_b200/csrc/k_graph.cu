@@ -89,7 +89,8 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_flatten(uint32_t n, uint32_t 
     uint32_t r = cc_find(label, i);
     label[i] = r;
     uint32_t m = meta[i].x;
-    if ((m & 0xffu) != MODE_STATIC && ((m >> 8) & BF_ACTIVE)) atomicOr(&flag[r], 1u); // island holds an awake body
+    // island holds an awake body; test first: a pile is ONE island and a million atomics on its flag would serialise
+    if ((m & 0xffu) != MODE_STATIC && ((m >> 8) & BF_ACTIVE) && !(((volatile uint32_t *)flag)[r] & 1u)) atomicOr(&flag[r], 1u);
 }
 
 // per-body copy of "my island is awake" so that pair kernels need no label/flag gathers

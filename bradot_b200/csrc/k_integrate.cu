@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(IT_THREADS) k_sleep_test(uint32_t n, float dt,
         }
         props[i].a2.w = st;
     }
-    if (!sleepy) atomicOr(&island_flag[root], 2u); // someone is awake
+    if (!sleepy && !(((volatile uint32_t *)island_flag)[root] & 2u)) atomicOr(&island_flag[root], 2u); // someone is awake
 }
 
 __global__ void __launch_bounds__(IT_THREADS) k_sleep_apply(uint32_t n, uint4 *__restrict__ meta, const uint32_t *__restrict__ island,
