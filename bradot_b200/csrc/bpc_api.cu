@@ -44,7 +44,7 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
     ctx->island.free_(); ctx->island_flag.free_(); ctx->shapes.free_(); ctx->meshes.free_(); ctx->mverts.free_();
     ctx->mplanes.free_(); ctx->medges.free_(); ctx->mfaces.free_(); ctx->mindex.free_(); ctx->d_spaces.free_();
     ctx->keys.free_(); ctx->keys_alt.free_(); ctx->vals.free_(); ctx->vals_alt.free_(); ctx->hist.free_();
-    ctx->leaf_min.free_(); ctx->leaf_max.free_(); ctx->nodes.free_(); ctx->node_parent.free_(); ctx->node_flag.free_();
+    ctx->leaf_min.free_(); ctx->leaf_max.free_(); ctx->nodes.free_(); ctx->node_parent.free_(); ctx->node_flag.free_(); ctx->node_maxleaf.free_();
     ctx->big_items.free_(); ctx->big_start.free_(); ctx->bounds.free_(); ctx->counters.free_(); ctx->pair_keys_raw.free_();
     for (int b = 0; b < 2; b++) {
         ctx->pair_keys[b].free_(); ctx->pair_hdr[b].free_(); ctx->cgeo[b].free_(); ctx->cacc[b].free_();

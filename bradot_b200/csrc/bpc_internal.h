@@ -184,6 +184,7 @@ struct bpc_context {
     DevBuf<float4> leaf_min, leaf_max; // sorted leaves: min.w = item id (bits), max.w = space (bits)
     DevBuf<float4> nodes;              // 4 float4 per internal node
     DevBuf<uint32_t> node_parent, node_flag;
+    DevBuf<uint32_t> node_maxleaf;     // per internal node and side: highest leaf index below it (all ones if a static leaf is below)
     DevBuf<uint32_t> big_items;        // static items with unbounded boxes (planes), brute-forced; grouped by space
     DevBuf<uint32_t> big_start;        // [n_spaces + 1] offsets of each space's run in big_items
     std::vector<uint32_t> h_space_of;  // host mirror: space of each body

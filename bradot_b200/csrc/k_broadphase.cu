@@ -152,10 +152,13 @@ __global__ void __launch_bounds__(BP_THREADS) k_build(int n, const uint64_t *__r
 // node layout (4 x float4): [lmin | left id] [lmax | left space range] [rmin | right id] [rmax | right space range]
 __global__ void __launch_bounds__(BP_THREADS) k_refit(int n, const float4 *__restrict__ leaf_min, const float4 *__restrict__ leaf_max,
                                                       const uint32_t *__restrict__ parent, uint32_t *__restrict__ flag,
-                                                      float4 *__restrict__ nodes) {
+                                                      float4 *__restrict__ nodes, const uint4 *__restrict__ meta, uint32_t *__restrict__ maxleaf) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     float4 bmin = leaf_min[t], bmax = leaf_max[t];
+    // Each dynamic pair is reported by the query with the LOWER leaf index, so a query may skip every subtree whose
+    // highest leaf index is not above its own; static leaves never query, so they must stay reachable for everyone.
+    uint32_t mk = (meta[__float_as_uint(bmin.w)].x & 0xffu) == MODE_STATIC ? 0xffffffffu : (uint32_t)t;
     uint32_t srange = __float_as_uint(bmax.w);
     uint32_t self = (uint32_t)t | LEAF_BIT; // child id as stored in the node: leaf index | LEAF_BIT
     uint32_t me = (uint32_t)(n - 1 + t);
@@ -167,6 +170,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_refit(int n, const float4 *__res
         float4 *nd = nodes + (size_t)pi * 4 + (right ? 2 : 0);
         nd[0] = make_float4(bmin.x, bmin.y, bmin.z, __uint_as_float(self));
         nd[1] = make_float4(bmax.x, bmax.y, bmax.z, __uint_as_float(srange));
+        maxleaf[(size_t)pi * 2 + (right ? 1 : 0)] = mk;
         __threadfence();
         uint32_t old = atomicAdd(&flag[pi], 1u);
         if (old == 0) break;
@@ -180,6 +184,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_refit(int n, const float4 *__res
         bmax.x = fmaxf(bmax.x, omax.x); bmax.y = fmaxf(bmax.y, omax.y); bmax.z = fmaxf(bmax.z, omax.z);
         uint32_t smin_ = min(srange & 0xffffu, osr & 0xffffu), smax_ = max(srange >> 16, osr >> 16);
         srange = smin_ | (smax_ << 16);
+        mk = max(mk, ((const volatile uint32_t *)maxleaf)[(size_t)pi * 2 + (right ? 0 : 1)]);
         self = pi;
         me = pi;
     }
@@ -202,7 +207,7 @@ __device__ __forceinline__ void emit_pair(uint64_t key, uint64_t *__restrict__ o
 }
 
 __global__ void __launch_bounds__(BP_THREADS) k_traverse(int n, const float4 *__restrict__ leaf_min, const float4 *__restrict__ leaf_max,
-                                                         const float4 *__restrict__ nodes, const uint4 *__restrict__ meta,
+                                                         const float4 *__restrict__ nodes, const uint32_t *__restrict__ maxleaf, const uint4 *__restrict__ meta,
                                                          const ItemBox *__restrict__ items, const uint32_t *__restrict__ big, const uint32_t *__restrict__ big_start,
                                                          uint64_t *__restrict__ out, uint32_t cap, uint32_t *__restrict__ counter) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -231,8 +236,9 @@ __global__ void __launch_bounds__(BP_THREADS) k_traverse(int n, const float4 *__
         float4 lmin = nd[0], lmax = nd[1], rmin = nd[2], rmax = nd[3];
         uint32_t lc = __float_as_uint(lmin.w), rc = __float_as_uint(rmin.w);
         uint32_t lsr = __float_as_uint(lmax.w), rsr = __float_as_uint(rmax.w);
-        bool hl = boxes_overlap(qmin, qmax, lmin, lmax) && qsp >= (lsr & 0xffffu) && qsp <= (lsr >> 16);
-        bool hr = boxes_overlap(qmin, qmax, rmin, rmax) && qsp >= (rsr & 0xffffu) && qsp <= (rsr >> 16);
+        uint2 ml = *(const uint2 *)(maxleaf + (size_t)node * 2);
+        bool hl = ml.x > (uint32_t)t && boxes_overlap(qmin, qmax, lmin, lmax) && qsp >= (lsr & 0xffffu) && qsp <= (lsr >> 16);
+        bool hr = ml.y > (uint32_t)t && boxes_overlap(qmin, qmax, rmin, rmax) && qsp >= (rsr & 0xffffu) && qsp <= (rsr >> 16);
 #pragma unroll
         for (int side = 0; side < 2; side++) {
             bool h = side ? hr : hl;
@@ -240,10 +246,9 @@ __global__ void __launch_bounds__(BP_THREADS) k_traverse(int n, const float4 *__
             if (h && (c & LEAF_BIT)) {
                 uint32_t lj = c & ~LEAF_BIT;
                 uint32_t j = __float_as_uint(leaf_min[lj].w);
-                if (j != qi) {
+                if (j != qi) { // the leaf-order rule above already made this the reporting side
                     uint4 jm = meta[j];
-                    bool jstatic = (jm.x & 0xffu) == MODE_STATIC;
-                    if ((jstatic || qi < j) && ((qm.y & jm.z) || (jm.y & qm.z))) {
+                    if ((qm.y & jm.z) || (jm.y & qm.z)) {
                         uint32_t a = min(qi, j), b = max(qi, j);
                         emit_pair(((uint64_t)a << 32) | b, out, cap, counter);
                     }
@@ -348,6 +353,7 @@ int bpc_build_tree(bpc_context *ctx) {
     ctx->nodes.reserve((size_t)n * 4, false, st);
     ctx->node_parent.reserve((size_t)n * 2, false, st);
     ctx->node_flag.reserve(n, false, st);
+    ctx->node_maxleaf.reserve((size_t)n * 2, false, st);
     ctx->bounds.reserve(2, false, st);
     uint32_t *bounds = (uint32_t *)ctx->bounds.p;
     k_bounds_init<<<1, 32, 0, st>>>(bounds);
@@ -366,7 +372,7 @@ int bpc_build_tree(bpc_context *ctx) {
         BPC_CHECK(cudaMemsetAsync(ctx->node_flag.p, 0, (size_t)n * sizeof(uint32_t), st));
         k_build<<<nblk(n - 1, BP_THREADS), BP_THREADS, 0, st>>>((int)n, ctx->keys.p, ctx->node_parent.p);
         k_refit<<<nblk(n, BP_THREADS), BP_THREADS, 0, st>>>((int)n, ctx->leaf_min.p, ctx->leaf_max.p, ctx->node_parent.p, ctx->node_flag.p,
-                                                            ctx->nodes.p);
+                                                            ctx->nodes.p, ctx->meta.p, ctx->node_maxleaf.p);
     }
     BPC_CHECK(cudaGetLastError());
     return 0;
@@ -382,7 +388,7 @@ int bpc_launch_broadphase(bpc_context *ctx) {
     for (int attempt = 0; attempt < 3; attempt++) {
         BPC_CHECK(cudaMemsetAsync(ctx->counters.p + CNT_PAIRS, 0, sizeof(uint32_t), st));
         if (n) {
-            k_traverse<<<nblk(n, BP_THREADS), BP_THREADS, 0, st>>>((int)n, ctx->leaf_min.p, ctx->leaf_max.p, ctx->nodes.p, ctx->meta.p,
+            k_traverse<<<nblk(n, BP_THREADS), BP_THREADS, 0, st>>>((int)n, ctx->leaf_min.p, ctx->leaf_max.p, ctx->nodes.p, ctx->node_maxleaf.p, ctx->meta.p,
                                                                    ctx->items.p, ctx->big_items.p, ctx->big_start.p, ctx->pair_keys_raw.p,
                                                                    (uint32_t)ctx->pair_cap, ctx->counters.p + CNT_PAIRS);
             ctx->launches += 1;
