@@ -86,7 +86,14 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_flatten(uint32_t n, uint32_t 
                                                            uint32_t *__restrict__ flag) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    uint32_t r = cc_find(label, i);
+    // Read-only walk: a path-halving find here could store a stale (non-root) ancestor into label[j] AFTER thread j
+    // had written its root, leaving j with a label that is not its island's root for the rest of the step.
+    uint32_t r = i;
+    while (true) {
+        uint32_t p = ((volatile uint32_t *)label)[r];
+        if (p == r) break;
+        r = p;
+    }
     label[i] = r;
     uint32_t m = meta[i].x;
     // island holds an awake body; test first: a pile is ONE island and a million atomics on its flag would serialise
