@@ -48,6 +48,9 @@ def build_scene(name, scale, rank=0, world=1):
     if name == "c3":
         n = max(3, int(round(100 * scale ** (1 / 3.0))))
         return scenes.mixed_pile(n), "C3: %d mixed box/sphere/capsule bodies" % n ** 3
+    if name == "c4":
+        chains = max(1, int(round(25000 * scale)))
+        return scenes.convex_chains(chains), "C4: %d convex hulls (64 distinct) in %d chains of 8 linked alternately by pin and hinge joints" % (chains * 8, chains)
     raise SystemExit("unknown scene " + name)
 
 
@@ -242,6 +245,14 @@ def cuda_arm(args):
         iters = sc.iterations
         # pre-solve 296 + 76 c bytes per pair, each solver iteration 296 + 108 c bytes per pair
         solve_bytes = pc * ((296 + 76 * cbar) + iters * (296 + 108 * cbar))
+        if len(sc.joints):  # a joint-iteration: 296 B + 64 B per Jacobian row (pin 3, hinge 6)
+            rows = np.where(sc.joints["type"] == 0, 3, 6).astype(np.float64)
+            solve_bytes += float(np.sum(iters * (296 + 64 * rows)))
+        # the metric's second half: broadphase + narrowphase achieved GB/s (260 B per body, 16 + 664 B per broadphase pair)
+        bp_ms = stage_ms["broadphase"] / max(1, stage_steps)
+        np_ms = stage_ms["narrowphase"] / max(1, stage_steps)
+        bpairs = acc["collision_pairs"] / k
+        bp_bytes, np_bytes = 260.0 * nb + 16.0 * bpairs, 664.0 * bpairs
         solve_ms = stage_ms["solve"] / max(1, stage_steps)
         peak, peak_src = peaks()
         achieved = solve_bytes / (solve_ms * 1e-3) / 1e9 if solve_ms > 0 else 0.0
@@ -264,6 +275,10 @@ def cuda_arm(args):
                          "peak_source": peak_src, "avg_launch_ms": solve_ms, "algorithmic_bytes_per_launch": solve_bytes,
                          "share_of_step": solve_ms / (sum(stage_ms.values()) / max(1, stage_steps)) if stage_steps else None},
             "stage_ms_per_step": {s: v / max(1, stage_steps) for s, v in stage_ms.items()},
+            "stage_gbs": {"broadphase": bp_bytes / (bp_ms * 1e-3) / 1e9 if bp_ms > 0 else None,
+                          "narrowphase": np_bytes / (np_ms * 1e-3) / 1e9 if np_ms > 0 else None,
+                          "broadphase+narrowphase": (bp_bytes + np_bytes) / ((bp_ms + np_ms) * 1e-3) / 1e9 if bp_ms + np_ms > 0 else None,
+                          "note": "algorithmic bytes of SURVEY.md 8(d) / stage time (CUDA events), this rank"},
         }
         if args.cpu_baseline:
             kc = min(args.steps, args.cpu_steps)

@@ -240,15 +240,20 @@ class PhysicsServerCUDA:
     # -- scene loading --------------------------------------------------------------------------
     def load_scene(self, sc, meshes=None):
         """Build every space / shape / body / joint of a scenes.Scene.  ``meshes`` maps a convex
-        shape index to its hull (Geometry3D::MeshData layout), e.g. from an oracle dump."""
+        shape index to its hull (Geometry3D::MeshData layout), e.g. the reference's own from an oracle dump; a convex
+        shape without an entry gets its hull from bradot_b200.hull (same conventions, Qhull underneath)."""
         for _ in range(sc.n_spaces):
             sp = self.space_create()
             self.space_set_param(sp, SPACE_PARAM_SOLVER_ITERATIONS, sc.iterations)
         for i, s in enumerate(sc.shapes):
             if s["type"] == scenes.SHAPE_CONVEX:
                 if meshes is None or i not in meshes:
-                    raise PhysicsError("convex shape %d needs its hull mesh (the engine side runs ConvexHullComputer)" % i)
-                self.convex_polygon_shape_create(meshes[i])
+                    from . import hull
+                    key = (int(s["vert_ofs"]), int(s["vert_cnt"]))
+                    mesh = hull.mesh_data(sc.verts[key[0]:key[0] + key[1]])
+                else:
+                    mesh = meshes[i]
+                self.convex_polygon_shape_create(mesh)
             else:
                 self.shape_create(int(s["type"]), s["p"])
         first = self.bodies_create(sc.bodies) if len(sc.bodies) else 0

@@ -121,3 +121,46 @@ def test_gloo_two_ranks_timing_reduction(tmp_path):
     line = [l for l in r.stdout.splitlines() if l.startswith("RESULT")][0].split()
     assert float(line[1]) == 150.0    # max over ranks
     assert float(line[2]) == 10.0     # all units accounted for once
+
+
+def test_hull_builder_matches_the_reference_hull_topology():
+    """bradot_b200.hull (used by bench.py for C4, where no engine builds the hulls) against the meshes the reference's
+    ConvexHullComputer produced for the same point clouds (tests/golden/chains12.bdmp): same faces (as clockwise
+    vertex loops), same edges with the same face on each side.  Vertices are matched by position: the reference's
+    integer hull moves them by ~5e-5."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden
+    from bradot_b200 import hull, server
+    make, _, _ = make_golden.FIXTURES["chains12"]
+    sc = make()
+    ref = server.meshes_from_dump(scenes.read_dump(os.path.join(ROOT, "tests", "golden", "chains12.bdmp")))
+
+    def topo(m, vmap):
+        fk = {}
+        for f, (o, c) in enumerate(m["faces"]):
+            loop = [int(vmap[j]) for j in m["index"][o:o + c]]
+            k = loop.index(min(loop))
+            fk[f] = tuple(loop[k:] + loop[:k])
+        edges = set()
+        for a, b, fa, fb in m["edges"]:
+            a, b = int(vmap[a]), int(vmap[b])
+            edges.add((a, b, fk[fa], fk[fb]) if a < b else (b, a, fk[fb], fk[fa]))
+        return set(fk.values()), edges
+
+    seen = 0
+    for i, s in enumerate(sc.shapes):
+        if s["type"] != scenes.SHAPE_CONVEX:
+            continue
+        m = hull.mesh_data(sc.verts[s["vert_ofs"]:s["vert_ofs"] + s["vert_cnt"]])
+        r = ref[i]
+        vmap = np.array([np.argmin(np.linalg.norm(r["verts"] - v, axis=1)) for v in m["verts"]])
+        assert len(set(vmap)) == len(r["verts"]) == len(m["verts"])
+        assert np.max(np.linalg.norm(r["verts"][vmap] - m["verts"], axis=1)) < 1e-3
+        assert topo(m, vmap) == topo(r, np.arange(len(r["verts"])))
+        for f in range(len(m["planes"])):   # outward normals, d = n.v
+            o, c = m["faces"][f]
+            assert np.allclose(m["verts"][m["index"][o:o + c]] @ m["planes"][f, :3], m["planes"][f, 3], atol=1e-5)
+            assert np.all(m["verts"] @ m["planes"][f, :3] <= m["planes"][f, 3] + 1e-5)
+        seen += 1
+    assert seen >= 3
