@@ -150,6 +150,7 @@ struct bpc_context {
     DevBuf<uint32_t> a_range; // [2 * n_bodies]: begin / end of each body's run (as A) in the previous pair list
     DevBuf<float> staging;    // packed per-body floats on their way to / from the host (bulk state I/O)
     DevBuf<uint32_t> np_work; // broadphase pairs that need the full narrowphase pass this step
+    DevBuf<uint32_t> np_cwork; // hull-against-hull pairs handed to the warp-per-pair kernel
     DevBuf<uint64_t> forced_keys;
 
     uint32_t n_bodies = 0;
@@ -231,7 +232,7 @@ struct bpc_context {
 };
 
 enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIVE = 4, CNT_ISLANDS = 5, CNT_CONTACTS = 6,
-       CNT_OVERFLOW = 7, CNT_ROUND = 8, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_N = 16 };
+       CNT_OVERFLOW = 7, CNT_ROUND = 8, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_N = 16 };
 
 #define BPC_CHECK(x)                                                                                  \
     do {                                                                                              \

@@ -6,7 +6,7 @@
 //                 manifold update.  Most broadphase pairs are box-overlap-only and never reach it.
 //   modules/bradot_physics_3d/bradot_body_pair_3d.cpp:264-317  BradotBodyPair3D::setup
 //   modules/bradot_physics_3d/bradot_step_3d.cpp:347-349       parallel _setup_constraint over all constraints
-#include "np_sat.cuh"
+#include "np_convex_warp.cuh"
 
 #define NP_THREADS 64
 
@@ -35,6 +35,7 @@ struct NpArgs {
     uint32_t n_except;
     uint32_t *counters;
     uint32_t *work;      // compacted pair indices for the full pass
+    uint32_t *cwork;     // hull-against-hull pairs for the warp-per-pair kernel
     const uint32_t *perm; // pair indices binned by shape-type pair (nullptr = identity)
     uint32_t n_work;
 };
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(256) k_type_keys(uint32_t n, const uint64_t *_
 
 __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    bool work = false;
+    bool work = false, cwork = false;
     if (t < a.n_pairs) {
         uint32_t k = a.perm ? a.perm[t] : t;
         uint64_t key = a.keys[k];
@@ -135,24 +136,38 @@ __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
                 Sh sa = load_shape_fast(a, ia, ma.x);
                 Sh sb = load_shape_fast(a, ib, mb.x);
                 V3 sep_axis = f4v(h.sep);
-                Manifold *none = nullptr;
-                bool collided = solve_static<true>(sa, xA, sb, xB, *none, &sep_axis);
                 nb |= (collide_A ? 0x200u : 0u) | (collide_B ? 0x400u : 0u);
-                // the full pass decides again and generates contacts; cached contacts must be validated even when apart
-                work = collided || count > 0;
+                if (sa.type == SH_CONVEX && sb.type == SH_CONVEX && cw_fits(sa.m) && cw_fits(sb.m)) {
+                    // three likely separating axes here; whatever they do not settle goes to the warp-per-pair kernel
+                    cwork = !cw_quick_separated(sa, xA, sb, xB, sep_axis) || count > 0;
+                } else {
+                    Manifold *none = nullptr;
+                    bool collided = solve_static<true>(sa, xA, sb, xB, *none, &sep_axis);
+                    // the full pass decides again and generates contacts; cached contacts must be validated even when apart
+                    work = collided || count > 0;
+                }
             }
-            if (!work) {
+            if (!work && !cwork) {
                 h.sep.w = __uint_as_float(nb);
                 a.hdr[k] = h;
             }
         }
     }
+    uint32_t lane = threadIdx.x & 31;
     uint32_t m = __ballot_sync(0xffffffffu, work);
-    if (!m) return;
-    uint32_t lane = threadIdx.x & 31, base = 0;
-    if (lane == 0) base = atomicAdd(&a.counters[CNT_WORK], __popc(m));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (work) a.work[base + __popc(m & ((1u << lane) - 1u))] = a.perm ? a.perm[t] : t;
+    if (m) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&a.counters[CNT_WORK], __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (work) a.work[base + __popc(m & ((1u << lane) - 1u))] = a.perm ? a.perm[t] : t;
+    }
+    m = __ballot_sync(0xffffffffu, cwork);
+    if (m) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&a.counters[CNT_CWORK], __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (cwork) a.cwork[base + __popc(m & ((1u << lane) - 1u))] = a.perm ? a.perm[t] : t;
+    }
 }
 
 __global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
@@ -213,6 +228,91 @@ __global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
     a.hdr[k] = h;
 }
 
+// One warp per hull-against-hull pair left undecided by k_pair_test: axis tests and support search across the lanes
+// (np_convex_warp.cuh), then lane 0 validates the cached manifold, clips and stores (as k_pair_setup does).
+__global__ void __launch_bounds__(CW_WARPS * 32) k_convex_warp(NpArgs a) {
+    __shared__ CwShared sh[CW_WARPS];
+    uint32_t lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
+    uint32_t w = blockIdx.x * CW_WARPS + wi;
+    if (w >= a.counters[CNT_CWORK]) return;
+    CwShared &s = sh[wi];
+    uint32_t k = a.cwork[w];
+    uint64_t key = a.keys[k];
+    uint32_t ia = (uint32_t)(key >> 32), ib = (uint32_t)key;
+    uint4 ma = a.meta[ia], mb = a.meta[ib];
+    uint32_t mode_a = ma.x & 0xffu, mode_b = mb.x & 0xffu;
+    PairHdr h = a.hdr[k];
+    BodyXf bxa = a.xf[ia], bxb = a.xf[ib];
+    M3 bA(f4v(bxa.r0), f4v(bxa.r1), f4v(bxa.r2)), bB(f4v(bxb.r0), f4v(bxb.r1), f4v(bxb.r2));
+    V3 offset_B = f4v(bxb.o) - f4v(bxa.o);
+    X3 xA = shape_world(a, ia, ma.x, bA, V3());
+    X3 xB = shape_world(a, ib, mb.x, bB, offset_B);
+    Sh sa = load_shape_fast(a, ia, ma.x);
+    Sh sb = load_shape_fast(a, ib, mb.x);
+    cw_stage(s, 0, sa.m, xA, lane);
+    cw_stage(s, 1, sb.m, xB, lane);
+    V3 sep_axis = f4v(h.sep), best_axis;
+    bool collided = cw_sat(s, sa.m, xA, sb.m, xB, sep_axis, lane, best_axis) && !(best_axis == V3(0.f, 0.f, 0.f));
+    if (collided) {
+        cw_supports(s, 0, sa.m, normalized(xform_inv(xA.b, -best_axis)), lane);
+        cw_supports(s, 1, sb.m, normalized(xform_inv(xB.b, best_axis)), lane);
+    }
+    if (lane != 0) return;
+    int count = __float_as_uint(h.sep.w) & 0xffu;
+    bool collide_A = (mode_a > MODE_KINEMATIC) && (mb.y & ma.z);
+    bool collide_B = (mode_b > MODE_KINEMATIC) && (ma.y & mb.z);
+    const SpaceParams sp = a.spaces[ma.w];
+    Manifold m;
+    m.bA = bA;
+    m.bB = bB;
+    m.offset_B = offset_B;
+    m.recycle2 = sp.recycle_radius * sp.recycle_radius;
+    m.count = count;
+    for (int c = 0; c < 4; c++) {
+        if (c < count) {
+            ContactGeo g = a.geo[(size_t)k * 4 + c];
+            ContactAcc ac = a.acc[(size_t)k * 4 + c];
+            m.la[c] = f4v(g.la);
+            m.lb[c] = f4v(g.lb);
+            m.n[c] = f4v(g.n);
+            m.used[c] = __float_as_uint(g.la.w) & 1u;
+            m.acc_tn[c] = ac.t_n;
+            m.acc_b[c] = make_float2(ac.b.x, ac.b.y);
+        } else {
+            m.used[c] = false;
+        }
+    }
+    manifold_validate(m, sp.max_separation);
+    if (collided) {
+        V3 pA[MAX_SUPPORTS], pB[MAX_SUPPORTS];
+        int nA = s.sup_n[0], nB = s.sup_n[1];
+        for (int i = 0; i < nA; i++) pA[i] = xform(xA, V3(s.sup[0][i][0], s.sup[0][i][1], s.sup[0][i][2]));
+        for (int i = 0; i < nB; i++) pB[i] = xform(xB, V3(s.sup[1][i][0], s.sup[1][i][1], s.sup[1][i][2]));
+        Collector cb;
+        cb.m = &m;
+        cb.swap = false;
+        cb.collided = true;
+        cb.prev_axis = &sep_axis;
+        cb.normal = best_axis;
+        sep_axis = best_axis;
+        if (nA >= 1 && nB >= 1) generate_contacts_from_supports(pA, nA, s.sup_t[0], pB, nB, s.sup_t[1], cb);
+    }
+    for (int c = 0; c < m.count; c++) {
+        ContactGeo g;
+        g.la = v4(m.la[c], __uint_as_float(m.used[c] ? 1u : 0u));
+        g.lb = v4(m.lb[c], 0.f);
+        g.n = v4(m.n[c], 0.f);
+        ContactAcc ac;
+        ac.t_n = m.acc_tn[c];
+        ac.b = make_float4(m.acc_b[c].x, m.acc_b[c].y, 0.f, 0.f);
+        a.geo[(size_t)k * 4 + c] = g;
+        a.acc[(size_t)k * 4 + c] = ac;
+    }
+    uint32_t nb = (uint32_t)m.count | (collided ? 0x100u : 0u) | (collide_A ? 0x200u : 0u) | (collide_B ? 0x400u : 0u);
+    h.sep = v4(sep_axis, __uint_as_float(nb));
+    a.hdr[k] = h;
+}
+
 int bpc_launch_narrowphase(bpc_context *ctx) {
     uint32_t n = ctx->n_pairs[ctx->cur];
     if (!n) return 0;
@@ -246,6 +346,16 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
         return -1;
     }
     a.work = ctx->np_work.p;
+    a.cwork = nullptr;
+    bool hulls = (ctx->shape_type_mask >> SH_CONVEX) & 1u;
+    if (hulls) {
+        ctx->np_cwork.reserve((size_t)n + 1, false, ctx->stream);
+        if (!ctx->np_cwork.p) {
+            ctx->err = "narrowphase: out of device memory";
+            return -1;
+        }
+        a.cwork = ctx->np_cwork.p;
+    }
     a.n_work = 0;
     a.perm = nullptr;
     uint32_t solid_types = ctx->shape_type_mask & ~(1u << SH_PLANE);
@@ -268,6 +378,10 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
     // the survivor count stays on the device: launch for the worst case, surplus threads exit at once
     k_pair_setup<<<(n + NP_THREADS - 1) / NP_THREADS, NP_THREADS, 0, ctx->stream>>>(a);
     ctx->launches += 2;
+    if (hulls) {
+        k_convex_warp<<<(n + CW_WARPS - 1) / CW_WARPS, CW_WARPS * 32, 0, ctx->stream>>>(a);
+        ctx->launches += 1;
+    }
     BPC_CHECK(cudaGetLastError());
     return 0;
 }
