@@ -17,7 +17,7 @@ import numpy as np
 from . import scenes
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbradot_physics_cuda.so")
+LIB_PATH = os.environ.get("BPC_LIBRARY", os.path.join(_HERE, "libbradot_physics_cuda.so"))  # override: A/B builds of the same ABI
 
 FIELD_TRANSFORM, FIELD_LINEAR_VELOCITY, FIELD_ANGULAR_VELOCITY, FIELD_ACTIVE = 0, 1, 2, 3
 FIELD_MASS_PROPS, FIELD_ITEM_BOX, FIELD_APPLIED_FORCE, FIELD_STILL_TIME = 4, 5, 6, 7
