@@ -232,7 +232,7 @@ struct bpc_context {
 };
 
 enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIVE = 4, CNT_ISLANDS = 5, CNT_CONTACTS = 6,
-       CNT_OVERFLOW = 7, CNT_ROUND = 8, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_N = 16 };
+       CNT_OVERFLOW = 7, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_ROUND = 20 /* 3 slots */, CNT_N = 32 };
 
 #define BPC_CHECK(x)                                                                                  \
     do {                                                                                              \

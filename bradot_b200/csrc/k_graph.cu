@@ -252,10 +252,13 @@ __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t
             }
         }
         uint32_t any = __syncthreads_or(left != 0);
-        if (threadIdx.x == 0 && any) atomicOr(&counters[CNT_ROUND + (round & 1)], 1u);
-        if (tid == 0) counters[CNT_ROUND + ((round + 1) & 1)] = 0; // reset the other parity slot for the next round
+        // "someone is left" flags rotate over three slots: the one cleared here for the next round was last read after the
+        // barrier two rounds back, which every CTA has left (with two slots a CTA still on its way to that read could see
+        // the cleared value, leave the loop alone and never reach the next barrier)
+        if (threadIdx.x == 0 && any) atomicOr(&counters[CNT_ROUND + round % 3], 1u);
+        if (tid == 0) counters[CNT_ROUND + (round + 1) % 3] = 0;
         grid.sync();
-        if (counters[CNT_ROUND + (round & 1)] == 0) break;
+        if (counters[CNT_ROUND + round % 3] == 0) break;
     }
 }
 
@@ -325,7 +328,7 @@ int bpc_launch_schedule(bpc_context *ctx) {
     BPC_CHECK(cudaMemsetAsync(ctx->body_best.p, 0, (size_t)n * 16, st));
     BPC_CHECK(cudaMemsetAsync(ctx->body_colmask.p, 0, (size_t)n * 8, st));
     BPC_CHECK(cudaMemsetAsync(ctx->color_start.p, 0, 2 * (MAX_COLORS + 4) * sizeof(uint32_t), st));
-    BPC_CHECK(cudaMemsetAsync(ctx->counters.p + CNT_ROUND, 0, 2 * sizeof(uint32_t), st));
+    BPC_CHECK(cudaMemsetAsync(ctx->counters.p + CNT_ROUND, 0, 3 * sizeof(uint32_t), st));
     {
         int per_sm = 0;
         BPC_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_color, GR_THREADS, 0));
