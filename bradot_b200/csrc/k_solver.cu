@@ -35,7 +35,8 @@ struct SvArgs {
     const uint32_t *n_groups;    // device scalar
     uint32_t serial_group;       // index of a group that must run on one thread (colour overflow), or 0xffffffff
     uint4 *info;
-    SolveContact *sc;
+    SolveContact *sc;     // contact c of slot s at sc[c * sc_stride + s]: the first contacts of a sweep are one dense stream
+    size_t sc_stride;
     const JointRec *joints;
     const JointSetup *jsetup;
     float dt, inv_dt, max_bias_av;
@@ -127,7 +128,7 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
             sc.n_mn = v4(n, 0.f);
             sc.ra_b = make_float4(0.f, 0.f, 0.f, 0.f);
             sc.rb_bo = make_float4(0.f, 0.f, 0.f, 0.f);
-            a.sc[(size_t)s * 4 + c] = sc;
+            a.sc[(size_t)c * a.sc_stride + s] = sc;
             continue;
         }
         V3 rA = gA - A.com;
@@ -151,7 +152,7 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
         sc.ra_b = v4(rA, cbias);
         sc.rb_bo = v4(rB, bounce);
         sc.b.w = 1.f;
-        a.sc[(size_t)s * 4 + c] = sc;
+        a.sc[(size_t)c * a.sc_stride + s] = sc;
         any = true;
         n_active++;
     }
@@ -166,7 +167,7 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
 __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
     uint4 inf = a.info[s];
     // first contact record requested together with the info word: its latency overlaps the body gathers
-    SolveContact first = a.sc[(size_t)s * 4];
+    SolveContact first = a.sc[s];
     if (!(inf.z & 0x800u)) return;
     uint32_t ia = inf.x, ib = inf.y;
     int count = inf.z & 0xffu;
@@ -177,7 +178,7 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
     load_body(a, ib, cB, B, f2, f3);
     bool touched = false;
     for (int c = 0; c < count; c++) {
-        SolveContact sc = c == 0 ? first : a.sc[(size_t)s * 4 + c];
+        SolveContact sc = c == 0 ? first : a.sc[(size_t)c * a.sc_stride + s];
         if (sc.b.w == 0.f) continue;
         bool active = false;
         V3 n = f4v(sc.n_mn), rA = f4v(sc.ra_b), rB = f4v(sc.rb_bo);
@@ -246,8 +247,8 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
             active = true;
         }
         sc.b.w = active ? 1.f : 0.f;
-        a.sc[(size_t)s * 4 + c].t_n = sc.t_n;
-        a.sc[(size_t)s * 4 + c].b = sc.b;
+        a.sc[(size_t)c * a.sc_stride + s].t_n = sc.t_n;
+        a.sc[(size_t)c * a.sc_stride + s].b = sc.b;
         touched = true;
     }
     if (touched) {
@@ -435,7 +436,7 @@ __device__ inline void finish_pair(const SvArgs &a, uint32_t s) {
     int count = inf.z & 0xffu;
     uint32_t k = inf.w;
     for (int c = 0; c < count; c++) {
-        SolveContact sc = a.sc[(size_t)s * 4 + c];
+        SolveContact sc = a.sc[(size_t)c * a.sc_stride + s];
         ContactAcc ac;
         ac.t_n = sc.t_n;
         ac.b = make_float4(sc.b.x, sc.b.y, 0.f, 0.f);
@@ -554,6 +555,7 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     }
     a.info = ctx->con_info.p;
     a.sc = ctx->scontacts.p;
+    a.sc_stride = maxc;
     a.joints = ctx->d_joints.p;
     a.jsetup = ctx->jsetup.p;
     a.dt = dt;
