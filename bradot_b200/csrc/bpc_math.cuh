@@ -23,6 +23,13 @@ struct V3 {
     BPC_HD float &operator[](int i) { return (&x)[i]; }
     BPC_HD const float &operator[](int i) const { return (&x)[i]; }
 };
+// component by a run-time index without taking the vector's address (operator[] pins it in local memory on the device)
+BPC_HD float comp(const V3 &v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : v.z); }
+BPC_HD void set_comp(V3 &v, int i, float f) {
+    v.x = i == 0 ? f : v.x;
+    v.y = i == 1 ? f : v.y;
+    v.z = i == 2 ? f : v.z;
+}
 BPC_HD V3 operator+(V3 a, V3 b) { return V3(a.x + b.x, a.y + b.y, a.z + b.z); }
 BPC_HD V3 operator-(V3 a, V3 b) { return V3(a.x - b.x, a.y - b.y, a.z - b.z); }
 BPC_HD V3 operator-(V3 a) { return V3(-a.x, -a.y, -a.z); }
@@ -66,7 +73,7 @@ struct M3 {
     V3 r[3];
     BPC_HD M3() { r[0] = V3(1.f, 0.f, 0.f); r[1] = V3(0.f, 1.f, 0.f); r[2] = V3(0.f, 0.f, 1.f); }
     BPC_HD M3(V3 a, V3 b, V3 c) { r[0] = a; r[1] = b; r[2] = c; }
-    BPC_HD V3 col(int i) const { return V3(r[0][i], r[1][i], r[2][i]); }
+    BPC_HD V3 col(int i) const { return V3(comp(r[0], i), comp(r[1], i), comp(r[2], i)); }
     BPC_HD void set_col(int i, V3 v) { r[0][i] = v.x; r[1][i] = v.y; r[2][i] = v.z; }
 };
 BPC_HD M3 m3_zero() { return M3(V3(), V3(), V3()); }

@@ -6,16 +6,22 @@
 #pragma once
 #include "np_shapes.cuh"
 
+// Per thread in k_pair_setup, in shared memory in the warp-per-pair kernel.  Plain 4-byte members and an odd size in
+// words, so that an array of these in shared memory spreads over the banks.
+struct A4 { float x, y, z, w; };
+struct A2 { float x, y; };
 struct Manifold {
     V3 la[4], lb[4], n[4];
-    float4 acc_tn[4]; // tangent xyz, normal
-    float2 acc_b[4];  // bias, bias_com
+    A4 acc_tn[4]; // tangent xyz, normal
+    A2 acc_b[4];  // bias, bias_com
     bool used[4];
     int count;
     M3 bA, bB;
     V3 offset_B;
     float recycle2;
+    float pad_to_odd_words;
 };
+static_assert(sizeof(Manifold) == 85 * 4, "Manifold must stay an odd number of words");
 
 // contact_added_callback: points are relative to A's origin.
 __device__ inline void manifold_add(Manifold &m, V3 pA, V3 pB) {
@@ -53,8 +59,8 @@ __device__ inline void manifold_add(Manifold &m, V3 pA, V3 pB) {
             m.lb[least] = local_B;
             m.n[least] = normal;
             m.used[least] = true;
-            m.acc_tn[least] = make_float4(0.f, 0.f, 0.f, 0.f);
-            m.acc_b[least] = make_float2(0.f, 0.f);
+            m.acc_tn[least] = A4{ 0.f, 0.f, 0.f, 0.f };
+            m.acc_b[least] = A2{ 0.f, 0.f };
         }
         return;
     }
@@ -63,8 +69,8 @@ __device__ inline void manifold_add(Manifold &m, V3 pA, V3 pB) {
     m.lb[k] = local_B;
     m.n[k] = normal;
     m.used[k] = true;
-    m.acc_tn[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-    m.acc_b[k] = make_float2(0.f, 0.f);
+    m.acc_tn[k] = A4{ 0.f, 0.f, 0.f, 0.f };
+    m.acc_b[k] = A2{ 0.f, 0.f };
 }
 
 __device__ inline void manifold_validate(Manifold &m, float max_sep) {
@@ -88,8 +94,8 @@ __device__ inline void manifold_validate(Manifold &m, float max_sep) {
                 t = m.la[i]; m.la[i] = m.la[l]; m.la[l] = t;
                 t = m.lb[i]; m.lb[i] = m.lb[l]; m.lb[l] = t;
                 t = m.n[i]; m.n[i] = m.n[l]; m.n[l] = t;
-                float4 a = m.acc_tn[i]; m.acc_tn[i] = m.acc_tn[l]; m.acc_tn[l] = a;
-                float2 b = m.acc_b[i]; m.acc_b[i] = m.acc_b[l]; m.acc_b[l] = b;
+                A4 a = m.acc_tn[i]; m.acc_tn[i] = m.acc_tn[l]; m.acc_tn[l] = a;
+                A2 b = m.acc_b[i]; m.acc_b[i] = m.acc_b[l]; m.acc_b[l] = b;
                 bool u = m.used[i]; m.used[i] = m.used[l]; m.used[l] = u;
             }
             i--;

@@ -252,7 +252,7 @@ __device__ inline void col_box_capsule(const Sh &a, const X3 &xa, const Sh &b, c
                 he.y *= (j * 2 - 1);
                 he.z *= (k * 2 - 1);
                 V3 point = xa.o;
-                for (int l = 0; l < 3; l++) point += xa.b.col(l) * he[l];
+                for (int l = 0; l < 3; l++) point += xa.b.col(l) * comp(he, l);
                 Pl pl;
                 pl.n = cyl_axis;
                 pl.d = 0.f;
@@ -431,27 +431,28 @@ __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, co
         if (ta > tb) return col_plane<TEST>(sb, xb, sa, xa, c, true);
         return col_plane<TEST>(sa, xa, sb, xb, c, false);
     }
-    const Sh *A = &sa, *B = &sb;
-    const X3 *XA = &xa, *XB = &xb;
-    if (ta > tb) {
-        A = &sb; B = &sa; XA = &xb; XB = &xa;
+    // ordered by shape type; swapped BY VALUE: pointers to whichever of two locals would pin all four in local memory
+    const bool swap = ta > tb;
+    const Sh A = swap ? sb : sa, B = swap ? sa : sb;
+    const X3 XA = swap ? xb : xa, XB = swap ? xa : xb;
+    if (swap) {
         uint32_t t = ta; ta = tb; tb = t;
         c.swap = true;
     }
     if (ta == SH_SPHERE) {
-        if (tb == SH_SPHERE) col_sphere_sphere<TEST>(*A, *XA, *B, *XB, c);
-        else if (tb == SH_BOX) col_sphere_box<TEST>(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CAPSULE) col_sphere_capsule<TEST>(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CONVEX) col_sphere_convex<TEST>(*A, *XA, *B, *XB, c);
+        if (tb == SH_SPHERE) col_sphere_sphere<TEST>(A, XA, B, XB, c);
+        else if (tb == SH_BOX) col_sphere_box<TEST>(A, XA, B, XB, c);
+        else if (tb == SH_CAPSULE) col_sphere_capsule<TEST>(A, XA, B, XB, c);
+        else if (tb == SH_CONVEX) col_sphere_convex<TEST>(A, XA, B, XB, c);
     } else if (ta == SH_BOX) {
-        if (tb == SH_BOX) col_box_box<TEST>(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CAPSULE) col_box_capsule<TEST>(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CONVEX) col_box_convex<TEST>(*A, *XA, *B, *XB, c);
+        if (tb == SH_BOX) col_box_box<TEST>(A, XA, B, XB, c);
+        else if (tb == SH_CAPSULE) col_box_capsule<TEST>(A, XA, B, XB, c);
+        else if (tb == SH_CONVEX) col_box_convex<TEST>(A, XA, B, XB, c);
     } else if (ta == SH_CAPSULE) {
-        if (tb == SH_CAPSULE) col_capsule_capsule<TEST>(*A, *XA, *B, *XB, c);
-        else if (tb == SH_CONVEX) col_capsule_convex<TEST>(*A, *XA, *B, *XB, c);
+        if (tb == SH_CAPSULE) col_capsule_capsule<TEST>(A, XA, B, XB, c);
+        else if (tb == SH_CONVEX) col_capsule_convex<TEST>(A, XA, B, XB, c);
     } else if (ta == SH_CONVEX && tb == SH_CONVEX) {
-        col_convex_convex<TEST>(*A, *XA, *B, *XB, c);
+        col_convex_convex<TEST>(A, XA, B, XB, c);
     }
     return c.collided;
 }

@@ -72,26 +72,29 @@ __device__ inline void project_range(const Sh &s, V3 axis, const X3 &xf, float &
 }
 
 __device__ inline void box_supports(V3 he, V3 n, V3 *sup, int &amount, int &type) {
-    const int next[3] = { 1, 2, 0 };
-    const int next2[3] = { 2, 0, 1 };
     for (int i = 0; i < 3; i++) {
-        float d = n[i]; // dot with a unit axis
+        float d = comp(n, i); // dot with a unit axis
         if ((double)fabsf(d) > FACE_SUPPORT_THRESHOLD) {
             bool neg = d < 0;
             amount = 4;
             type = FEATURE_FACE;
             V3 point;
-            point[i] = he[i];
-            int i_n = next[i], i_n2 = next2[i];
-            const float sign[4][2] = { { -1.0f, 1.0f }, { 1.0f, 1.0f }, { 1.0f, -1.0f }, { -1.0f, -1.0f } };
+            set_comp(point, i, comp(he, i));
+            int i_n = i == 2 ? 0 : i + 1, i_n2 = i == 0 ? 2 : i - 1;
+            const float h_n = comp(he, i_n), h_n2 = comp(he, i_n2);
+            V3 q[4];
+#pragma unroll
             for (int j = 0; j < 4; j++) {
-                point[i_n] = sign[j][0] * he[i_n];
-                point[i_n2] = sign[j][1] * he[i_n2];
-                sup[j] = neg ? -point : point;
+                // signs of the four corners: (-,+) (+,+) (+,-) (-,-)
+                const float s0 = (j == 1 || j == 2) ? 1.0f : -1.0f, s1 = (j < 2) ? 1.0f : -1.0f;
+                set_comp(point, i_n, s0 * h_n);
+                set_comp(point, i_n2, s1 * h_n2);
+                q[j] = neg ? -point : point;
             }
             if (neg) {
-                V3 t = sup[1]; sup[1] = sup[2]; sup[2] = t;
-                t = sup[0]; sup[0] = sup[3]; sup[3] = t;
+                sup[0] = q[3]; sup[1] = q[2]; sup[2] = q[1]; sup[3] = q[0];
+            } else {
+                sup[0] = q[0]; sup[1] = q[1]; sup[2] = q[2]; sup[3] = q[3];
             }
             return;
         }
@@ -99,15 +102,15 @@ __device__ inline void box_supports(V3 he, V3 n, V3 *sup, int &amount, int &type
     }
     const double lower = edge_support_threshold_lower();
     for (int i = 0; i < 3; i++) {
-        if ((double)fabsf(n[i]) < lower) {
+        if ((double)fabsf(comp(n, i)) < lower) {
             amount = 2;
             type = FEATURE_EDGE;
-            int i_n = next[i], i_n2 = next2[i];
+            int i_n = i == 2 ? 0 : i + 1, i_n2 = i == 0 ? 2 : i - 1;
             V3 point = he;
-            if (n[i_n] < 0) point[i_n] = -point[i_n];
-            if (n[i_n2] < 0) point[i_n2] = -point[i_n2];
+            if (comp(n, i_n) < 0) set_comp(point, i_n, -comp(point, i_n));
+            if (comp(n, i_n2) < 0) set_comp(point, i_n2, -comp(point, i_n2));
             sup[0] = point;
-            point[i] = -point[i];
+            set_comp(point, i, -comp(point, i));
             sup[1] = point;
             return;
         }
