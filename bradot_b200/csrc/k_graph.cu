@@ -204,7 +204,8 @@ __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t
                                                       const PairHdr *__restrict__ hdr, const JointRec *__restrict__ joints,
                                                       const uint4 *__restrict__ meta, uint32_t *__restrict__ list,
                                                       uint32_t *__restrict__ color, unsigned long long *__restrict__ best,
-                                                      unsigned long long *__restrict__ colmask, uint32_t *__restrict__ counters) {
+                                                      unsigned long long *__restrict__ colmask, uint32_t *__restrict__ counters,
+                                                      uint2 *__restrict__ ab) {
     cg::grid_group grid = cg::this_grid();
     uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     // joints are appended to the list here (they are always solved)
@@ -220,6 +221,7 @@ __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t
     for (uint32_t s = tid; s < n; s += nth) {
         uint32_t id = list[s], a, b;
         con_bodies(id, n_pairs, keys, hdr, joints, meta, a, b);
+        ab[s] = make_uint2(a, b); // the rounds read the two bodies from here: one coalesced load instead of two gathers
         unsigned long long ticket = (1ull << 32) | hash32(id);
         if (a != 0xffffffffu) atomicMax(&bestv[1][a], ticket);
         if (b != 0xffffffffu) atomicMax(&bestv[1][b], ticket);
@@ -231,8 +233,9 @@ __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t
         uint32_t left = 0;
         for (uint32_t s = tid; s < n; s += nth) {
             if (color[s] != 0xffffffffu) continue;
-            uint32_t id = list[s], a, b;
-            con_bodies(id, n_pairs, keys, hdr, joints, meta, a, b);
+            uint32_t id = list[s];
+            uint2 bodies = ab[s];
+            uint32_t a = bodies.x, b = bodies.y;
             uint32_t hsh = hash32(id);
             unsigned long long ticket = ((unsigned long long)round << 32) | hsh;
             bool win = (a == 0xffffffffu || cur[a] == ticket) && (b == 0xffffffffu || cur[b] == ticket);
@@ -320,9 +323,15 @@ int bpc_launch_schedule(bpc_context *ctx) {
     ctx->con_list.reserve(maxc, false, st);
     ctx->con_color.reserve(maxc, false, st);
     ctx->con_sorted.reserve(maxc, false, st);
+    ctx->con_info.reserve(maxc, false, st);
     ctx->body_best.reserve((size_t)n * 2, false, st);
     ctx->body_colmask.reserve(n, false, st);
     ctx->color_start.reserve(2 * (MAX_COLORS + 4), false, st);
+    if (!ctx->con_list.p || !ctx->con_color.p || !ctx->con_sorted.p || !ctx->con_info.p || !ctx->body_best.p || !ctx->body_colmask.p ||
+        !ctx->color_start.p || ctx->con_info.cap < maxc || ctx->con_list.cap < maxc) {
+        ctx->err = "schedule: out of device memory";
+        return -1;
+    }
     if (np) k_con_collect<<<nblk(np, GR_THREADS), GR_THREADS, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->pair_keys[ctx->cur].p, ctx->meta.p,
                                                                         ctx->island.p, ctx->island_flag.p, ctx->con_list.p, ctx->counters.p);
     BPC_CHECK(cudaMemsetAsync(ctx->body_best.p, 0, (size_t)n * 16, st));
@@ -341,7 +350,8 @@ int bpc_launch_schedule(bpc_context *ctx) {
         const uint4 *meta = ctx->meta.p;
         uint32_t *list = ctx->con_list.p, *color = ctx->con_color.p, *counters = ctx->counters.p;
         unsigned long long *best = (unsigned long long *)ctx->body_best.p, *colmask = (unsigned long long *)ctx->body_colmask.p;
-        void *args[] = { &np, &nj, &n, &keys, &hdr, &joints, &meta, &list, &color, &best, &colmask, &counters };
+        uint2 *ab = (uint2 *)ctx->con_info.p; // the solver's per-slot records are not live yet: scratch for the colouring
+        void *args[] = { &np, &nj, &n, &keys, &hdr, &joints, &meta, &list, &color, &best, &colmask, &counters, &ab };
         BPC_CHECK(cudaLaunchCooperativeKernel((void *)k_color, grid, block, args, 0, st));
     }
     uint32_t *start = ctx->color_start.p, *cursor = ctx->color_start.p + (MAX_COLORS + 4);
