@@ -255,6 +255,14 @@ def cuda_arm(args):
         bp_bytes, np_bytes = 260.0 * nb + 16.0 * bpairs, 664.0 * bpairs
         solve_ms = stage_ms["solve"] / max(1, stage_steps)
         peak, peak_src = peaks()
+        traffic, traffic_src = None, None
+        try:  # DRAM bytes of one k_solve launch from the committed ncu capture of this scene (profiles/), if there is one
+            with open(os.path.join(ROOT, "profiles", "k_solve_traffic.json")) as f:
+                t = json.load(f).get(args.scene if args.scale >= 1.0 else "")
+            if t:
+                traffic, traffic_src = t["traffic_bytes"], "ncu capture at step %d (%d colliding pairs): %s" % (t["step"], t["contact_pairs"], t["capture"])
+        except (OSError, ValueError, KeyError):
+            pass
         achieved = solve_bytes / (solve_ms * 1e-3) / 1e9 if solve_ms > 0 else 0.0
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -271,7 +279,7 @@ def cuda_arm(args):
             "gpu_launches": acc["launches"],
             "clocks": sampler.summary(),
             "roofline": {"bound": "hbm", "kernel": "k_solve (pre-solve + %d Gauss-Seidel sweeps, cooperative launch)" % iters,
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src, "avg_launch_ms": solve_ms, "algorithmic_bytes_per_launch": solve_bytes,
                          "share_of_step": solve_ms / (sum(stage_ms.values()) / max(1, stage_steps)) if stage_steps else None},
             "stage_ms_per_step": {s: v / max(1, stage_steps) for s, v in stage_ms.items()},
