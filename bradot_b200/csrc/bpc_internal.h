@@ -272,6 +272,7 @@ int bpc_launch_integrate_forces(bpc_context *ctx, float dt);
 int bpc_launch_integrate_velocities(bpc_context *ctx, float dt);
 int bpc_launch_refresh_bodies(bpc_context *ctx, uint32_t first, uint32_t n, int passes);
 int bpc_launch_broadphase(bpc_context *ctx);
+int bpc_build_tree(bpc_context *ctx); // LBVH over the current stored boxes (also used by the space queries)
 int bpc_launch_islands(bpc_context *ctx);
 int bpc_launch_narrowphase(bpc_context *ctx);
 int bpc_launch_solver(bpc_context *ctx, float dt);

@@ -1,0 +1,465 @@
+// Space queries on the GPU-resident LBVH, batched: one thread per ray.
+//   modules/bradot_physics_3d/bradot_space_3d.cpp:42-60     _can_collide_with
+//   modules/bradot_physics_3d/bradot_space_3d.cpp:109-207   BradotPhysicsDirectSpaceState3D::intersect_ray
+//   modules/bradot_physics_3d/bradot_shape_3d.cpp:130-140 (world boundary) :279-285 (sphere) :421-429 (box)
+//     :555-619 (capsule) :979-1028 (convex polygon)          intersect_segment / intersect_point
+//   core/math/geometry_3d.h:86-276   segment_intersects_triangle / _sphere / _cylinder
+//   core/math/aabb.cpp:189-252       AABB::intersects_segment      core/math/plane.cpp:119-137  Plane::intersects_segment
+//
+// The reference culls the segment against its BVH (stored, expanded boxes) and then asks every candidate shape; the
+// answer is the hit of least `normal . point`.  Candidates only have to be a superset of the shapes the segment really
+// meets, so any conservative segment/box test over OUR tree gives the same answer (except for exact ties, which the
+// reference breaks by its own tree order).
+#include "../../include/bradot_physics_cuda.h"
+#include "np_shapes.cuh"
+
+#define Q_THREADS 128
+#define Q_LEAF_BIT 0x80000000u
+
+struct QArgs {
+    uint32_t n_rays, n_tree, space;
+    const float *rays; // n x (from xyz, to xyz)
+    bpc_ray_result *out;
+    uint32_t mask, flags;
+    const float4 *nodes;
+    const float4 *leaf_min;
+    const uint4 *meta;
+    const BodyXf *xf;
+    const BodyXf *shape_xf;
+    const float4 *shape_p;
+    const MeshRec *meshes;
+    const float4 *mverts;
+    const float4 *mplanes;
+    const uint2 *mfaces;
+    const uint32_t *mindex;
+    const uint32_t *big;
+    const uint32_t *big_start;
+};
+
+struct RayHit {
+    V3 point, normal;
+};
+
+// AABB::intersects_segment on a box given as (begin, end) per axis
+__device__ inline bool q_box_segment(V3 bmin, V3 bmax, V3 from, V3 to, V3 *r_point, V3 *r_normal) {
+    float mn = 0.f, mx = 1.f;
+    int axis = 0;
+    float sign = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        float seg_from = comp(from, i), seg_to = comp(to, i);
+        float box_begin = comp(bmin, i), box_end = comp(bmax, i);
+        float cmin, cmax, csign;
+        if (seg_from < seg_to) {
+            if (seg_from > box_end || seg_to < box_begin) return false;
+            float length = seg_to - seg_from;
+            cmin = (seg_from < box_begin) ? ((box_begin - seg_from) / length) : 0.f;
+            cmax = (seg_to > box_end) ? ((box_end - seg_from) / length) : 1.f;
+            csign = -1.0f;
+        } else {
+            if (seg_to > box_end || seg_from < box_begin) return false;
+            float length = seg_to - seg_from;
+            cmin = (seg_from > box_end) ? (box_end - seg_from) / length : 0.f;
+            cmax = (seg_to < box_begin) ? (box_begin - seg_from) / length : 1.f;
+            csign = 1.0f;
+        }
+        if (cmin > mn) {
+            mn = cmin;
+            axis = i;
+            sign = csign;
+        }
+        if (cmax < mx) mx = cmax;
+        if (mx < mn) return false;
+    }
+    if (r_normal) {
+        V3 n;
+        set_comp(n, axis, sign);
+        *r_normal = n;
+    }
+    if (r_point) *r_point = from + (to - from) * mn;
+    return true;
+}
+
+__device__ inline bool q_sphere_segment(V3 from, V3 to, V3 sphere_pos_in, float radius, RayHit &h) {
+    V3 sphere_pos = sphere_pos_in - from;
+    V3 rel = to - from;
+    float rel_l = length(rel);
+    if (rel_l < (float)BPC_CMP_EPSILON) return false;
+    V3 normal = rel / rel_l;
+    float sphere_d = dot(normal, sphere_pos);
+    V3 on_ray = normal * sphere_d;
+    float ray_distance = sqrtf(distance_squared(sphere_pos, on_ray));
+    if (ray_distance >= radius) return false;
+    float inters_d2 = radius * radius - ray_distance * ray_distance;
+    float inters_d = sphere_d;
+    if (inters_d2 >= (float)BPC_CMP_EPSILON) inters_d -= sqrtf(inters_d2);
+    if (inters_d < 0 || inters_d > rel_l) return false;
+    V3 result = from + normal * inters_d;
+    h.point = result;
+    h.normal = normalized(result - sphere_pos_in);
+    return true;
+}
+
+// Geometry3D::segment_intersects_cylinder with the axis along y (p_cylinder_axis = 1)
+__device__ inline bool q_cylinder_segment(V3 from, V3 to, float height, float radius, RayHit &h) {
+    V3 rel = to - from;
+    float rel_l = length(rel);
+    if (rel_l < (float)BPC_CMP_EPSILON) return false;
+    V3 cylinder_axis(0.f, 1.f, 0.f);
+    V3 normal = rel / rel_l;
+    V3 crs = cross(normal, cylinder_axis);
+    float crs_l = length(crs);
+    V3 axis_dir;
+    if (crs_l < (float)BPC_CMP_EPSILON) axis_dir = V3(0.f, 0.f, 1.f); // side axis (1 + 1) % 3
+    else axis_dir = crs / crs_l;
+    float dist = dot(axis_dir, from);
+    if (dist >= radius) return false;
+    float w2 = radius * radius - dist * dist;
+    if (w2 < (float)BPC_CMP_EPSILON) return false;
+    float size[2] = { sqrtf(w2), height * 0.5f };
+    V3 side_dir = normalized(cross(axis_dir, cylinder_axis));
+    float from2[2] = { dot(side_dir, from), from.y };
+    float to2[2] = { dot(side_dir, to), to.y };
+    float mn = 0.f, mx = 1.f;
+    int axis = -1;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        float seg_from = from2[i], seg_to = to2[i];
+        float box_begin = -size[i], box_end = size[i];
+        float cmin, cmax;
+        if (seg_from < seg_to) {
+            if (seg_from > box_end || seg_to < box_begin) return false;
+            float length = seg_to - seg_from;
+            cmin = (seg_from < box_begin) ? ((box_begin - seg_from) / length) : 0.f;
+            cmax = (seg_to > box_end) ? ((box_end - seg_from) / length) : 1.f;
+        } else {
+            if (seg_to > box_end || seg_from < box_begin) return false;
+            float length = seg_to - seg_from;
+            cmin = (seg_from > box_end) ? (box_end - seg_from) / length : 0.f;
+            cmax = (seg_to < box_begin) ? (box_begin - seg_from) / length : 1.f;
+        }
+        if (cmin > mn) {
+            mn = cmin;
+            axis = i;
+        }
+        if (cmax < mx) mx = cmax;
+        if (mx < mn) return false;
+    }
+    V3 result = from + (rel * mn);
+    V3 res_normal = result;
+    if (axis == 0) {
+        res_normal.y = 0.f;
+    } else {
+        res_normal.z = 0.f; // (axis + 1) % 3 and the one after it
+        res_normal.x = 0.f;
+    }
+    h.point = result;
+    h.normal = normalized(res_normal);
+    return true;
+}
+
+__device__ inline bool q_triangle_segment(V3 from, V3 to, V3 v0, V3 v1, V3 v2, V3 &res) {
+    V3 rel = to - from;
+    V3 e1 = v1 - v0, e2 = v2 - v0;
+    V3 hh = cross(rel, e2);
+    float a = dot(e1, hh);
+    if (is_zero_approx(a)) return false;
+    float f = 1.0f / a;
+    V3 s = from - v0;
+    float u = f * dot(s, hh);
+    if ((u < 0.0f) || (u > 1.0f)) return false;
+    V3 q = cross(s, e1);
+    float v = f * dot(rel, q);
+    if ((v < 0.0f) || (u + v > 1.0f)) return false;
+    float t = f * dot(e2, q);
+    if (t > (float)BPC_CMP_EPSILON && t <= 1.0f) {
+        res = from + rel * t;
+        return true;
+    }
+    return false;
+}
+
+struct QShape {
+    uint32_t type;
+    float4 p;
+    MeshRec mesh;
+};
+
+__device__ inline bool q_shape_point_inside(const QArgs &a, const QShape &s, V3 p) {
+    switch (s.type) {
+        case SH_PLANE: return (dot(V3(s.p.x, s.p.y, s.p.z), p) - s.p.w) < 0;
+        case SH_SPHERE: return length(p) < s.p.x;
+        case SH_BOX: return fabsf(p.x) < s.p.x && fabsf(p.y) < s.p.y && fabsf(p.z) < s.p.z;
+        case SH_CAPSULE: {
+            float radius = s.p.x, height = s.p.y;
+            if (fabsf(p.y) < height * 0.5f - radius) return length(V3(p.x, 0.f, p.z)) < radius;
+            V3 q = p;
+            q.y = fabsf(q.y) - height * 0.5f + radius;
+            return length(q) < radius;
+        }
+        default: {
+            for (uint32_t i = 0; i < s.mesh.face_cnt; i++) {
+                float4 pl = a.mplanes[s.mesh.face_ofs + i];
+                if (dot(V3(pl.x, pl.y, pl.z), p) - pl.w >= 0) return false;
+            }
+            return true;
+        }
+    }
+}
+
+__device__ inline bool q_shape_segment(const QArgs &a, const QShape &s, V3 from, V3 to, RayHit &h) {
+    switch (s.type) {
+        case SH_PLANE: { // Plane::intersects_segment
+            V3 n(s.p.x, s.p.y, s.p.z);
+            V3 segment = from - to;
+            float den = dot(n, segment);
+            if (is_zero_approx(den)) return false;
+            float dist = (dot(n, from) - s.p.w) / den;
+            if (dist < -(float)BPC_CMP_EPSILON || dist > (1.0f + (float)BPC_CMP_EPSILON)) return false;
+            dist = -dist;
+            h.point = from + segment * dist;
+            h.normal = n;
+            return true;
+        }
+        case SH_SPHERE: return q_sphere_segment(from, to, V3(), s.p.x, h);
+        case SH_BOX: {
+            V3 he(s.p.x, s.p.y, s.p.z);
+            V3 pos = -he, size = he * 2.0f;
+            return q_box_segment(pos, pos + size, from, to, &h.point, &h.normal);
+        }
+        case SH_CAPSULE: {
+            float radius = s.p.x, height = s.p.y;
+            V3 norm = normalized(to - from);
+            float min_d = 1e20f;
+            bool collision = false;
+            RayHit aux;
+            if (q_cylinder_segment(from, to, height - radius * 2.0f, radius, aux)) {
+                float d = dot(norm, aux.point);
+                if (d < min_d) {
+                    min_d = d;
+                    h = aux;
+                    collision = true;
+                }
+            }
+            if (q_sphere_segment(from, to, V3(0.f, height * 0.5f - radius, 0.f), radius, aux)) {
+                float d = dot(norm, aux.point);
+                if (d < min_d) {
+                    min_d = d;
+                    h = aux;
+                    collision = true;
+                }
+            }
+            if (q_sphere_segment(from, to, V3(0.f, height * -0.5f + radius, 0.f), radius, aux)) {
+                float d = dot(norm, aux.point);
+                if (d < min_d) {
+                    min_d = d;
+                    h = aux;
+                    collision = true;
+                }
+            }
+            return collision;
+        }
+        default: { // convex polygon: fan of every face that looks towards the ray
+            V3 n = to - from;
+            float mn = 1e20f;
+            bool col = false;
+            for (uint32_t i = 0; i < s.mesh.face_cnt; i++) {
+                float4 pl = a.mplanes[s.mesh.face_ofs + i];
+                V3 fn(pl.x, pl.y, pl.z);
+                if (dot(fn, n) > 0) continue;
+                uint2 f = a.mfaces[s.mesh.face_ofs + i];
+                V3 v0 = f4v(a.mverts[s.mesh.vert_ofs + a.mindex[f.x]]);
+                for (uint32_t j = 1; j + 1 < f.y; j++) {
+                    V3 v1 = f4v(a.mverts[s.mesh.vert_ofs + a.mindex[f.x + j]]);
+                    V3 v2 = f4v(a.mverts[s.mesh.vert_ofs + a.mindex[f.x + j + 1]]);
+                    V3 result;
+                    if (q_triangle_segment(from, to, v0, v1, v2, result)) {
+                        float d = dot(n, result);
+                        if (d < mn) {
+                            mn = d;
+                            h.point = result;
+                            h.normal = fn;
+                            col = true;
+                        }
+                        break;
+                    }
+                }
+            }
+            return col;
+        }
+    }
+}
+
+struct RayBest {
+    float min_d;
+    bool collided;
+    uint32_t body;
+    V3 point, normal;
+};
+
+// one candidate of the loop at bradot_space_3d.cpp:131-187; returns true when the search must stop (hit_from_inside)
+__device__ inline bool q_ray_candidate(const QArgs &a, uint32_t j, V3 begin, V3 end, V3 normal, RayBest &best) {
+    uint4 m = a.meta[j];
+    if (m.w != a.space) return false;
+    if (!(m.y & a.mask)) return false; // _can_collide_with: layer & mask (bodies only exist here)
+    BodyXf bx = a.xf[j];
+    X3 xf(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
+    // get_inv_transform(): Transform3D::inverse() once a step has moved the body (bradot_body_3d.cpp:735),
+    // affine_inverse() for a body that was only ever placed (:306)
+    X3 inv_body;
+    if ((m.x & 0xffu) == MODE_STATIC) {
+        inv_body = affine_inverse(xf);
+    } else {
+        inv_body.b = transposed(xf.b);
+        inv_body.o = xform(inv_body.b, -xf.o);
+    }
+    X3 inv_xform = inv_body, to_world = xf;
+    if (!((m.x >> 8) & BF_SHAPE_IDENT)) {
+        BodyXf sx = a.shape_xf[j];
+        X3 sxf(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+        inv_xform = affine_inverse(sxf) * inv_body;
+        to_world = xf * sxf;
+    }
+    V3 local_from = xform(inv_xform, begin), local_to = xform(inv_xform, end);
+    QShape s;
+    s.type = m.x >> 24;
+    s.p = a.shape_p[j];
+    if (s.type == SH_CONVEX) s.mesh = a.meshes[__float_as_uint(s.p.x)];
+    if (q_shape_point_inside(a, s, local_from)) {
+        if (a.flags & 1u) { // hit_from_inside
+            best.min_d = 0.f;
+            best.point = begin;
+            best.normal = V3();
+            best.body = j;
+            best.collided = true;
+            return true;
+        }
+        return false;
+    }
+    RayHit h;
+    if (q_shape_segment(a, s, local_from, local_to, h)) {
+        V3 p = xform(to_world, h.point);
+        float ld = dot(normal, p);
+        if (ld < best.min_d) {
+            best.min_d = ld;
+            best.point = p;
+            best.normal = normalized(xform_inv(inv_xform.b, h.normal));
+            best.body = j;
+            best.collided = true;
+        }
+    }
+    return false;
+}
+
+__global__ void __launch_bounds__(Q_THREADS) k_intersect_rays(QArgs a) {
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= a.n_rays) return;
+    V3 begin(a.rays[r * 6 + 0], a.rays[r * 6 + 1], a.rays[r * 6 + 2]), end(a.rays[r * 6 + 3], a.rays[r * 6 + 4], a.rays[r * 6 + 5]);
+    V3 normal = normalized(end - begin);
+    RayBest best;
+    best.min_d = 1e10f;
+    best.collided = false;
+    best.body = 0xffffffffu;
+    bool done = false;
+    for (uint32_t k = a.big_start[a.space], ke = a.big_start[a.space + 1]; k < ke && !done; k++) done = q_ray_candidate(a, a.big[k], begin, end, normal, best);
+    const float grow = 1e-4f; // the box test only nominates candidates: err on the generous side
+    if (!done && a.n_tree == 1) {
+        q_ray_candidate(a, __float_as_uint(a.leaf_min[0].w), begin, end, normal, best);
+    } else if (!done && a.n_tree > 1) {
+        uint32_t stack[96];
+        int sp = 0;
+        uint32_t node = 0;
+        while (true) {
+            const float4 *nd = a.nodes + (size_t)node * 4;
+            float4 lmin = nd[0], lmax = nd[1], rmin = nd[2], rmax = nd[3];
+            uint32_t child[2] = { __float_as_uint(lmin.w), __float_as_uint(rmin.w) };
+            uint32_t srange[2] = { __float_as_uint(lmax.w), __float_as_uint(rmax.w) };
+            bool hit[2];
+            hit[0] = a.space >= (srange[0] & 0xffffu) && a.space <= (srange[0] >> 16) &&
+                     q_box_segment(V3(lmin.x - grow, lmin.y - grow, lmin.z - grow), V3(lmax.x + grow, lmax.y + grow, lmax.z + grow), begin, end, nullptr, nullptr);
+            hit[1] = a.space >= (srange[1] & 0xffffu) && a.space <= (srange[1] >> 16) &&
+                     q_box_segment(V3(rmin.x - grow, rmin.y - grow, rmin.z - grow), V3(rmax.x + grow, rmax.y + grow, rmax.z + grow), begin, end, nullptr, nullptr);
+#pragma unroll
+            for (int side = 0; side < 2; side++) {
+                if (hit[side] && (child[side] & Q_LEAF_BIT) && !done) {
+                    uint32_t lj = child[side] & ~Q_LEAF_BIT;
+                    done = q_ray_candidate(a, __float_as_uint(a.leaf_min[lj].w), begin, end, normal, best);
+                }
+            }
+            if (done) break;
+            bool il = hit[0] && !(child[0] & Q_LEAF_BIT), ir = hit[1] && !(child[1] & Q_LEAF_BIT);
+            if (il) {
+                if (ir && sp < 96) stack[sp++] = child[1];
+                node = child[0];
+            } else if (ir) {
+                node = child[1];
+            } else {
+                if (sp == 0) break;
+                node = stack[--sp];
+            }
+        }
+    }
+    bpc_ray_result o;
+    o.hit = best.collided ? 1 : 0;
+    o.body = best.collided ? (int)best.body : -1;
+    o.position[0] = best.point.x; o.position[1] = best.point.y; o.position[2] = best.point.z;
+    o.normal[0] = best.normal.x; o.normal[1] = best.normal.y; o.normal[2] = best.normal.z;
+    if (!best.collided) {
+        o.position[0] = o.position[1] = o.position[2] = 0.f;
+        o.normal[0] = o.normal[1] = o.normal[2] = 0.f;
+    }
+    a.out[r] = o;
+}
+
+extern "C" int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *from_to, unsigned collision_mask, int flags,
+                                        bpc_ray_result *out) {
+    if (!ctx) return -1;
+    if (space < 0 || (size_t)space >= ctx->spaces.size()) {
+        ctx->err = "bpc_space_intersect_rays: no such space";
+        return -1;
+    }
+    if (n < 0 || (n > 0 && (!from_to || !out))) {
+        ctx->err = "bpc_space_intersect_rays: bad arguments";
+        return -1;
+    }
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    // the tree of the last step was built from the boxes the bodies had BEFORE they moved: rebuild from the current ones
+    if (bpc_build_tree(ctx)) return -1;
+    size_t in_floats = (size_t)n * 6, out_floats = (size_t)n * (sizeof(bpc_ray_result) / sizeof(float));
+    ctx->staging.reserve(in_floats + out_floats + 16, false, st);
+    if (!ctx->staging.p) {
+        ctx->err = "bpc_space_intersect_rays: out of device memory";
+        return -1;
+    }
+    float *d_in = ctx->staging.p;
+    bpc_ray_result *d_out = (bpc_ray_result *)(ctx->staging.p + ((in_floats + 3) & ~(size_t)3));
+    BPC_CHECK(cudaMemcpyAsync(d_in, from_to, in_floats * sizeof(float), cudaMemcpyHostToDevice, st));
+    QArgs a;
+    a.n_rays = (uint32_t)n;
+    a.n_tree = ctx->n_tree;
+    a.space = (uint32_t)space;
+    a.rays = d_in;
+    a.out = d_out;
+    a.mask = collision_mask;
+    a.flags = (uint32_t)flags;
+    a.nodes = ctx->nodes.p;
+    a.leaf_min = ctx->leaf_min.p;
+    a.meta = ctx->meta.p;
+    a.xf = ctx->xf.p;
+    a.shape_xf = ctx->shape_xf.p;
+    a.shape_p = ctx->shape_p.p;
+    a.meshes = ctx->meshes.p;
+    a.mverts = ctx->mverts.p;
+    a.mplanes = ctx->mplanes.p;
+    a.mfaces = ctx->mfaces.p;
+    a.mindex = ctx->mindex.p;
+    a.big = ctx->big_items.p;
+    a.big_start = ctx->big_start.p;
+    k_intersect_rays<<<(n + Q_THREADS - 1) / Q_THREADS, Q_THREADS, 0, st>>>(a);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaMemcpyAsync(out, d_out, (size_t)n * sizeof(bpc_ray_result), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}

@@ -36,7 +36,7 @@ EXPORTS = [
     "bpc_shape_create", "bpc_shape_create_convex", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
     "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
-    "bpc_sort_u64_noalloc", "bpc_noalloc_last_error",
+    "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
 
@@ -48,6 +48,9 @@ class Stats(ctypes.Structure):
 
 class PhysicsError(RuntimeError):
     pass
+
+
+RAY_RESULT_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("position", "<f4", 3), ("normal", "<f4", 3)])
 
 
 def load_library(path=LIB_PATH):
@@ -73,6 +76,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_body_count.argtypes = [vp]
     lib.bpc_joints_create.argtypes = [vp, vp, ci]
     lib.bpc_step.argtypes = [vp, cf]
+    lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
     lib.bpc_synchronize.argtypes = [vp]
     lib.bpc_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
     lib.bpc_pair_count.argtypes = [vp]
@@ -226,6 +230,14 @@ class PhysicsServerCUDA:
         pf = np.ascontiguousarray(pf, np.float32).reshape(-1, 3)
         cf = np.ascontiguousarray(cf, np.float32).reshape(-1, 4, 16)
         self._check(self.lib.bpc_pairs_write(self.ctx, len(ids), _ptr(ids), _ptr(pf), _ptr(cf)))
+
+    def intersect_rays(self, from_to, space=0, collision_mask=0xFFFFFFFF, hit_from_inside=False):
+        """Batched PhysicsDirectSpaceState3D.intersect_ray: returns (hit bool[n], body int32[n], position (n,3), normal (n,3))."""
+        r = np.ascontiguousarray(from_to, np.float32).reshape(-1, 6)
+        out = np.zeros(len(r), RAY_RESULT_DT)
+        self._check(self.lib.bpc_space_intersect_rays(self.ctx, int(space), len(r), _ptr(r), ctypes.c_uint(collision_mask),
+                                                      1 if hit_from_inside else 0, _ptr(out)))
+        return out["hit"] != 0, out["body"].copy(), out["position"].copy(), out["normal"].copy()
 
     def set_solve_order(self, order):
         o = np.ascontiguousarray(order, np.int32).reshape(-1, 3)

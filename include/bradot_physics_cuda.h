@@ -130,6 +130,24 @@ int bpc_pairs_write(bpc_context *ctx, int n_pairs, const int32_t *pair_ids, cons
  * n = 0 returns to the default scheduling. */
 int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order);
 
+/* ---- space queries
+ * PhysicsDirectSpaceState3D::intersect_ray (servers/physics_server_3d.h:164-186; implementation
+ * modules/bradot_physics_3d/bradot_space_3d.cpp:109-207), batched: one call answers n rays against the current state of
+ * one space -- closest hit along each segment, bodies whose collision layer meets collision_mask, a shape the ray starts
+ * inside is ignored unless BPC_RAY_HIT_FROM_INSIDE.  from_to: n x (from xyz, to xyz), host; out: n records, host.
+ * `body` is the body slot (what the engine module maps back to a RID / ObjectID), -1 for a miss.
+ * Not in this round: exclude lists, areas, pick_ray, face_index (no concave shapes yet). */
+typedef struct bpc_ray_result {
+    int32_t hit;
+    int32_t body;
+    float position[3];
+    float normal[3];
+} bpc_ray_result;
+#define BPC_RAY_HIT_FROM_INSIDE 1
+#define BPC_RAY_HIT_BACK_FACES 2 /* accepted; only concave shapes look at it */
+int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *from_to, unsigned collision_mask, int flags,
+                             bpc_ray_result *out);
+
 /* ---- utilities exposed for tests and tools */
 /* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */
 int bpc_sort_u64(bpc_context *ctx, const uint64_t *keys_in, uint64_t *keys_out, int n);

@@ -11,7 +11,9 @@
 //   modules/bradot_physics_3d/bradot_physics_server_3d.cpp:1632  BradotPhysicsServer3D::step
 //   modules/bradot_physics_3d/bradot_step_3d.cpp:186              BradotStep3D::step
 //
-// usage: oracle_step <scene.bscn> [--steps N] [--dump out.bdmp] [--dump-from A] [--dump-every K]
+// usage: oracle_step <scene.bscn> [--steps N] [--dump out.bdmp] [--dump-from A] [--dump-every K] [--rays rays.bin]
+//   rays.bin: uint32 n, then n x (from xyz, to xyz) float32; every dumped step also holds "rays" (n,8): hit, body
+//   index, position xyz, normal xyz of PhysicsDirectSpaceState3D::intersect_ray in space 0 (mask 0xffffffff)
 //                    [--threads T] [--warmup W] [--quiet]
 // Timing JSON goes to stdout (one line).
 
@@ -251,6 +253,41 @@ static void dump_step(Dump &d, World &w, int step) {
 	d.arr("solve_order", step, "i4", { (uint64_t)order.size() / 3, 3 }, order.data(), order.size() * 4);
 }
 
+// PhysicsDirectSpaceState3D::intersect_ray (bradot_space_3d.cpp:109-191) for every ray of the file, space 0
+static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &rays) {
+	if (rays.empty()) {
+		return;
+	}
+	PhysicsDirectSpaceState3D *ds = w.ps->space_get_direct_state(w.spaces[0]);
+	std::map<RID, int> rid_index;
+	for (size_t i = 0; i < w.bodies.size(); i++) {
+		rid_index[w.bodies[i]] = (int)i;
+	}
+	size_t n = rays.size() / 6;
+	std::vector<float> out(n * 8, 0.f);
+	for (size_t i = 0; i < n; i++) {
+		PhysicsDirectSpaceState3D::RayParameters rp;
+		rp.from = Vector3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]);
+		rp.to = Vector3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+		rp.collision_mask = 0xffffffffu;
+		PhysicsDirectSpaceState3D::RayResult rr;
+		bool hit = ds && ds->intersect_ray(rp, rr);
+		out[i * 8 + 0] = hit ? 1.f : 0.f;
+		out[i * 8 + 1] = -1.f;
+		if (hit) {
+			auto it = rid_index.find(rr.rid);
+			out[i * 8 + 1] = it == rid_index.end() ? -1.f : (float)it->second;
+			out[i * 8 + 2] = rr.position.x;
+			out[i * 8 + 3] = rr.position.y;
+			out[i * 8 + 4] = rr.position.z;
+			out[i * 8 + 5] = rr.normal.x;
+			out[i * 8 + 6] = rr.normal.y;
+			out[i * 8 + 7] = rr.normal.z;
+		}
+	}
+	d.arr("rays", step, "f4", { (uint64_t)n, 8 }, out.data(), out.size() * 4);
+}
+
 static void dump_meshes(Dump &d, World &w) {
 	// convex hull meshes as the reference built them (ConvexHullComputer, bradot_shape_3d.cpp:1099)
 	for (size_t i = 0; i < w.shapes.size(); i++) {
@@ -316,7 +353,7 @@ int main(int argc, char **argv) {
 	}
 	const char *scene_path = argv[1];
 	int steps = 1, dump_from = 0, dump_every = 1, threads = -1, warmup = 0;
-	const char *dump_path = nullptr;
+	const char *dump_path = nullptr, *rays_path = nullptr;
 	for (int i = 2; i < argc; i++) {
 		std::string a = argv[i];
 		if (a == "--steps") {
@@ -331,9 +368,26 @@ int main(int argc, char **argv) {
 			threads = atoi(argv[++i]);
 		} else if (a == "--warmup") {
 			warmup = atoi(argv[++i]);
+		} else if (a == "--rays") {
+			rays_path = argv[++i];
 		}
 	}
 
+	std::vector<float> rays;
+	if (rays_path) {
+		FILE *rf = fopen(rays_path, "rb");
+		uint32_t nr = 0;
+		if (!rf || fread(&nr, 4, 1, rf) != 1) {
+			fprintf(stderr, "cannot read %s\n", rays_path);
+			return 2;
+		}
+		rays.resize((size_t)nr * 6);
+		if (fread(rays.data(), 4, rays.size(), rf) != rays.size()) {
+			fprintf(stderr, "short ray file\n");
+			return 2;
+		}
+		fclose(rf);
+	}
 	FILE *sf = fopen(scene_path, "rb");
 	if (!sf) {
 		fprintf(stderr, "cannot open %s\n", scene_path);
@@ -495,6 +549,7 @@ int main(int argc, char **argv) {
 		}
 		if (d.f && s >= dump_from && ((s - dump_from) % dump_every) == 0) {
 			dump_step(d, w, s);
+			dump_rays(d, w, s, rays);
 		}
 	}
 	auto t1 = std::chrono::steady_clock::now();

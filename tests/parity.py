@@ -19,15 +19,26 @@ def have_oracle():
     return os.path.exists(ORACLE) and os.access(ORACLE, os.X_OK)
 
 
-def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None):
-    """Step `sc` with the reference; returns (timing dict, dump dict)."""
+def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays=None):
+    """Step `sc` with the reference; returns (timing dict, dump dict).  `rays` (n, 6) float32 from/to: every dumped step
+    also holds ("rays", step) = the reference's intersect_ray answers in space 0."""
     d = tempfile.mkdtemp(prefix="bpc_oracle_")
     scn = os.path.join(d, "scene.bscn")
     dmp = keep or os.path.join(d, "out.bdmp")
     sc.write(scn)
     cmd = [ORACLE, scn, "--steps", str(steps), "--dump", dmp, "--dump-from", str(dump_from), "--dump-every", str(dump_every),
            "--threads", str(threads)]
+    rays_path = None
+    if rays is not None:
+        rays_path = os.path.join(d, "rays.bin")
+        r6 = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        with open(rays_path, "wb") as f:
+            f.write(np.uint32(len(r6)).tobytes())
+            f.write(r6.tobytes())
+        cmd += ["--rays", rays_path]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=1200)
+    if rays_path:
+        os.remove(rays_path)
     if r.returncode != 0:
         raise RuntimeError("oracle_step failed: %s" % r.stderr[-2000:])
     info = json.loads(r.stdout.strip().splitlines()[-1])

@@ -1,0 +1,80 @@
+"""Space queries: batched intersect_ray on the GPU-resident LBVH against the reference's
+PhysicsDirectSpaceState3D::intersect_ray (oracle/_ref/oracle_step --rays) on the same state."""
+import numpy as np
+import pytest
+
+import parity
+from bradot_b200 import scenes, server
+
+pytestmark = pytest.mark.gpu
+
+POS_TOL = 1e-4   # metres, on positions of order 1-10 (the reference's own fp32 chain: world -> local -> world)
+NRM_TOL = 1e-4
+
+
+def _rays(n, seed, half, top):
+    rng = np.random.default_rng(seed)
+    frm = rng.uniform(-half, half, (n, 3))
+    frm[:, 1] = rng.uniform(0.05, top, n)
+    to = frm + rng.normal(size=(n, 3)) * half
+    return np.concatenate([frm, to], 1).astype(np.float32)
+
+
+def _compare(sc, rays, steps, check):
+    _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1, rays=rays)
+    ps = parity.new_server(sc, dump)
+    seen_hits = 0
+    for k in check:
+        parity.load_state(ps, dump, k)
+        hit, body, pos, nrm = ps.intersect_rays(rays)
+        ref = dump[("rays", k)]
+        rhit = ref[:, 0] > 0
+        # a ray that grazes a shape within rounding may flip; everything else must agree exactly on hit and body
+        same = hit == rhit
+        assert same.mean() > 0.999, (k, int((~same).sum()))
+        both = hit & rhit
+        rbody = ref[:, 1].astype(np.int64)
+        agree = body[both] == rbody[both]
+        assert agree.mean() > 0.999, (k, int((~agree).sum()))
+        sel = np.nonzero(both)[0][agree]
+        assert np.max(np.abs(pos[sel] - ref[sel, 2:5])) < POS_TOL, k
+        assert np.max(np.abs(nrm[sel] - ref[sel, 5:8])) < NRM_TOL, k
+        seen_hits += len(sel)
+    ps.finish()
+    return seen_hits
+
+
+def test_intersect_rays_mixed_pile_boxes_spheres_capsules_planes():
+    parity_needed()
+    sc = scenes.mixed_pile(5, half=3.5)
+    assert _compare(sc, _rays(4000, 5, 4.0, 9.0), 60, [1, 20, 40, 59]) > 4000
+
+
+def test_intersect_rays_convex_hulls():
+    parity_needed()
+    sc = scenes.convex_pile(4)
+    assert _compare(sc, _rays(4000, 6, 4.0, 8.0), 50, [1, 25, 49]) > 2000
+
+
+def test_intersect_rays_edge_cases():
+    sc = scenes.spheres_container(3, 3, 3, half=1.75)
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc)
+    hit, body, pos, nrm = ps.intersect_rays(np.zeros((0, 6), np.float32))
+    assert len(hit) == 0
+    # degenerate segment (from == to), a ray that misses everything, a ray from far above straight down onto the floor
+    rays = np.array([[0, 5, 0, 0, 5, 0], [100, 100, 100, 101, 100, 100], [1.6, 50, 1.6, 1.6, -1, 1.6]], np.float32)
+    hit, body, pos, nrm = ps.intersect_rays(rays)
+    assert not hit[0] and not hit[1] and body[1] == -1
+    assert hit[2] and abs(pos[2, 1]) < 1e-5 and np.allclose(nrm[2], [0, 1, 0])
+    # collision mask 0 sees nothing; an unknown space is refused
+    hit, _, _, _ = ps.intersect_rays(rays, collision_mask=0)
+    assert not hit.any()
+    with pytest.raises(server.PhysicsError):
+        ps.intersect_rays(rays, space=7)
+    ps.finish()
+
+
+def parity_needed():
+    if not parity.have_oracle():
+        pytest.skip("oracle/_ref/oracle_step not built")
