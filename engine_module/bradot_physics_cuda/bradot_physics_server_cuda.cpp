@@ -140,6 +140,72 @@ RID BradotPhysicsServerCUDA::space_create() {
 	return space_owner.make_rid(space);
 }
 
+PhysicsDirectSpaceState3D *BradotPhysicsServerCUDA::space_get_direct_state(RID p_space) {
+	// same contract as the reference (bradot_physics_server_3d.cpp:189-197): one object per space, owned by the server
+	Space *space = space_owner.get_or_null(p_space);
+	ERR_FAIL_NULL_V(space, nullptr);
+	if (!space->direct_state) {
+		space->direct_state = memnew(BradotPhysicsDirectSpaceStateCUDA);
+		space->direct_state->server = this;
+		space->direct_state->space_handle = space->handle;
+	}
+	return space->direct_state;
+}
+
+int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit) {
+	ERR_FAIL_NULL_V(server, 0);
+	ERR_FAIL_COND_V(p_from_to.size() % 2, 0);
+	server->_flush_pending();
+	int n = p_from_to.size() / 2;
+	LocalVector<float> in;
+	in.resize(n * 6);
+	for (int i = 0; i < n * 2; i++) {
+		in[i * 3 + 0] = p_from_to[i].x;
+		in[i * 3 + 1] = p_from_to[i].y;
+		in[i * 3 + 2] = p_from_to[i].z;
+	}
+	LocalVector<bpc_ray_result> out;
+	out.resize(n);
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_rays(server->ctx, space_handle, n, in.ptr(), p_collision_mask, p_hit_from_inside ? BPC_RAY_HIT_FROM_INSIDE : 0, out.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	r_results.resize(n);
+	r_hit.resize(n);
+	int hits = 0;
+	for (int i = 0; i < n; i++) {
+		r_hit[i] = out[i].hit != 0 && out[i].body >= 0 && (uint32_t)out[i].body < server->body_of_slot.size();
+		if (!r_hit[i]) {
+			continue;
+		}
+		hits++;
+		RayResult &r = r_results[i];
+		r.position = Vector3(out[i].position[0], out[i].position[1], out[i].position[2]);
+		r.normal = Vector3(out[i].normal[0], out[i].normal[1], out[i].normal[2]);
+		r.rid = server->body_of_slot[out[i].body]->self;
+		r.collider_id = ObjectID(); // body_attach_object_instance_id is not carried yet
+		r.collider = nullptr;
+		r.shape = 0;
+		r.face_index = -1;
+	}
+	return hits;
+}
+
+bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_parameters, RayResult &r_result) {
+	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.pick_ray, false,
+			"BradotPhysicsCUDA: intersect_ray with exclude lists, areas or pick_ray is not supported yet.");
+	if (!p_parameters.collide_with_bodies) {
+		return false;
+	}
+	Vector<Vector3> ft;
+	ft.push_back(p_parameters.from);
+	ft.push_back(p_parameters.to);
+	LocalVector<RayResult> res;
+	LocalVector<bool> hit;
+	if (intersect_rays_batch(ft, p_parameters.collision_mask, p_parameters.hit_from_inside, res, hit) != 1) {
+		return false;
+	}
+	r_result = res[0];
+	return true;
+}
+
 void BradotPhysicsServerCUDA::space_set_active(RID p_space, bool p_active) {
 	Space *space = space_owner.get_or_null(p_space);
 	ERR_FAIL_NULL(space);
@@ -414,6 +480,9 @@ void BradotPhysicsServerCUDA::free(RID p_rid) {
 		memdelete(b);
 	} else if (space_owner.owns(p_rid)) {
 		Space *s = space_owner.get_or_null(p_rid);
+		if (s->direct_state) {
+			memdelete(s->direct_state);
+		}
 		space_owner.free(p_rid);
 		memdelete(s);
 	} else if (joint_owner.owns(p_rid)) {
@@ -469,6 +538,10 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 			ERR_FAIL_COND_MSG(first < 0, bpc_last_error(ctx));
 			for (uint32_t i = 0; i < uploaded.size(); i++) {
 				uploaded[i]->slot = first + i;
+				if (body_of_slot.size() <= (uint32_t)(first + i)) {
+					body_of_slot.resize(first + i + 1);
+				}
+				body_of_slot[first + i] = uploaded[i];
 			}
 		}
 		pending_bodies.clear();

@@ -18,8 +18,31 @@
 
 #define BPC_UNSUPPORTED(m_name) WARN_PRINT_ONCE("BradotPhysicsCUDA: " m_name "() is not supported by this backend yet.")
 
+class BradotPhysicsServerCUDA;
+
+// PhysicsDirectSpaceState3D of one space (servers/physics_server_3d.h:123-214; reference implementation
+// modules/bradot_physics_3d/bradot_space_3d.h:45-62).  intersect_ray runs on the GPU (bpc_space_intersect_rays, one
+// ray per call here; intersect_rays_batch answers many at once); the shape queries are "next" rows and answer "nothing".
+class BradotPhysicsDirectSpaceStateCUDA : public PhysicsDirectSpaceState3D {
+	BRCLASS(BradotPhysicsDirectSpaceStateCUDA, PhysicsDirectSpaceState3D);
+
+public:
+	BradotPhysicsServerCUDA *server = nullptr;
+	int space_handle = -1;
+
+	virtual bool intersect_ray(const RayParameters &p_parameters, RayResult &r_result) override;
+	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit);
+	virtual int intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) override { BPC_UNSUPPORTED("intersect_point"); return 0; }
+	virtual int intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) override { BPC_UNSUPPORTED("intersect_shape"); return 0; }
+	virtual bool cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info = nullptr) override { BPC_UNSUPPORTED("cast_motion"); return false; }
+	virtual bool collide_shape(const ShapeParameters &p_parameters, Vector3 *r_results, int p_result_max, int &r_result_count) override { BPC_UNSUPPORTED("collide_shape"); r_result_count = 0; return false; }
+	virtual bool rest_info(const ShapeParameters &p_parameters, ShapeRestInfo *r_info) override { BPC_UNSUPPORTED("rest_info"); return false; }
+	virtual Vector3 get_closest_point_to_object_volume(RID p_object, const Vector3 p_point) const override { BPC_UNSUPPORTED("get_closest_point_to_object_volume"); return p_point; }
+};
+
 class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	BRCLASS(BradotPhysicsServerCUDA, PhysicsServer3D);
+	friend class BradotPhysicsDirectSpaceStateCUDA;
 
 	struct Shape {
 		ShapeType type = SHAPE_SPHERE;
@@ -29,6 +52,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	struct Space {
 		int handle = -1;
 		bool active = false;
+		BradotPhysicsDirectSpaceStateCUDA *direct_state = nullptr;
 		real_t params[8] = { 0.01, 0.05, 0.01, 0.8, 0.1, Math::deg_to_rad(8.0), 0.5, 16 };
 	};
 	struct Body {
@@ -59,6 +83,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	bool active = true;
 	bool flushing_queries = false;
 	LocalVector<Body *> pending_bodies;
+	LocalVector<Body *> body_of_slot; // bpc body index -> body (what a query result is mapped back through)
 	LocalVector<Joint *> pending_joints;
 	bpc_stats last_stats = {};
 
@@ -84,6 +109,7 @@ public:
 	virtual bool space_is_active(RID p_space) const override;
 	virtual void space_set_param(RID p_space, SpaceParameter p_param, real_t p_value) override;
 	virtual real_t space_get_param(RID p_space, SpaceParameter p_param) const override;
+	virtual PhysicsDirectSpaceState3D *space_get_direct_state(RID p_space) override;
 	// bodies
 	virtual RID body_create() override;
 	virtual void body_set_space(RID p_body, RID p_space) override;

@@ -173,6 +173,26 @@ int main(int argc, char **argv) {
 		Transform3D t = ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM);
 		printf("%s[%.9g, %.9g, %.9g]", i ? ", " : "", t.origin.x, t.origin.y, t.origin.z);
 	}
+	printf("], \"rays\": [");
+	// PhysicsDirectSpaceState3D::intersect_ray through the RID API: straight down onto the first bodies
+	PhysicsDirectSpaceState3D *ds = ps->space_get_direct_state(space_r[0]);
+	int n_rays = body_r.size() < 16 ? (int)body_r.size() : 16;
+	for (int i = 0; ds && i < n_rays; i++) {
+		Transform3D t = ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM);
+		PhysicsDirectSpaceState3D::RayParameters rp;
+		rp.from = Vector3(t.origin.x, 30.0, t.origin.z);
+		rp.to = Vector3(t.origin.x, -1.0, t.origin.z);
+		PhysicsDirectSpaceState3D::RayResult rr;
+		bool hit = ds->intersect_ray(rp, rr);
+		int idx = -1;
+		for (size_t k = 0; hit && k < body_r.size(); k++) {
+			if (body_r[k] == rr.rid) {
+				idx = (int)k;
+				break;
+			}
+		}
+		printf("%s[%d, %d, %.9g, %.9g, %.9g]", i ? ", " : "", hit ? 1 : 0, idx, hit ? rr.position.x : 0.0, hit ? rr.position.y : 0.0, hit ? rr.position.z : 0.0);
+	}
 	printf("]}\n");
 	fflush(stdout);
 	ps->finish();

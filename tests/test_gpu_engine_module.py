@@ -33,7 +33,17 @@ def test_engine_module_matches_direct_c_abi(tmp_path):
         ps.step(sc.dt)
     direct = ps.bodies_read(server.FIELD_TRANSFORM)[:, 9:12]
     st = ps.stats()
+    # PhysicsDirectSpaceState3D::intersect_ray through the RID API == the batched C-ABI query on the same state
+    eng_rays = np.array(out["rays"], np.float64)
+    n = len(eng_rays)
+    ft = np.zeros((n, 6), np.float32)
+    ft[:, 0], ft[:, 1], ft[:, 2] = direct[:n, 0], 30.0, direct[:n, 2]
+    ft[:, 3], ft[:, 4], ft[:, 5] = direct[:n, 0], -1.0, direct[:n, 2]
+    hit, body, pos, _ = ps.intersect_rays(ft)
     ps.finish()
+    assert n == min(16, len(sc.bodies)) and hit.all() and np.array_equal(eng_rays[:, 0] != 0, hit)
+    assert np.array_equal(eng_rays[:, 1].astype(np.int64), body.astype(np.int64))
+    assert np.array_equal(eng_rays[:, 2:5].astype(np.float32), pos)
     assert engine.shape == direct.shape
     assert np.array_equal(engine, direct), float(np.abs(engine - direct).max())
     assert out["collision_pairs"] == st["collision_pairs"] and out["active_objects"] == st["active_objects"]
