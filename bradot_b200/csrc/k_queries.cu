@@ -411,6 +411,136 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_rays(QArgs a) {
     a.out[r] = o;
 }
 
+// BradotPhysicsDirectSpaceState3D::intersect_point (bradot_space_3d.cpp:62-107): every body whose shape holds the point,
+// up to max_results per point (which ones survive the cut follows OUR tree order, the reference's follows its own).
+struct PArgs {
+    QArgs q;
+    uint32_t max_results;
+    int32_t *counts;
+    int32_t *bodies; // n x max_results
+};
+
+__device__ inline void q_point_candidate(const PArgs &a, uint32_t j, V3 point, uint32_t r, int &cc) {
+    if (cc >= (int)a.max_results) return;
+    uint4 m = a.q.meta[j];
+    if (m.w != a.q.space || !(m.y & a.q.mask)) return;
+    BodyXf bx = a.q.xf[j];
+    X3 xf(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
+    if (!((m.x >> 8) & BF_SHAPE_IDENT)) {
+        BodyXf sx = a.q.shape_xf[j];
+        xf = xf * X3(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+    }
+    X3 inv_xform = affine_inverse(xf);
+    QShape s;
+    s.type = m.x >> 24;
+    s.p = a.q.shape_p[j];
+    if (s.type == SH_CONVEX) s.mesh = a.q.meshes[__float_as_uint(s.p.x)];
+    if (!q_shape_point_inside(a.q, s, xform(inv_xform, point))) return;
+    a.bodies[(size_t)r * a.max_results + cc] = (int32_t)j;
+    cc++;
+}
+
+__global__ void __launch_bounds__(Q_THREADS) k_intersect_points(PArgs a) {
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= a.q.n_rays) return;
+    V3 p(a.q.rays[r * 3 + 0], a.q.rays[r * 3 + 1], a.q.rays[r * 3 + 2]);
+    int cc = 0;
+    for (uint32_t k = a.q.big_start[a.q.space], ke = a.q.big_start[a.q.space + 1]; k < ke; k++) q_point_candidate(a, a.q.big[k], p, r, cc);
+    const float grow = 1e-4f;
+    if (a.q.n_tree == 1) {
+        q_point_candidate(a, __float_as_uint(a.q.leaf_min[0].w), p, r, cc);
+    } else if (a.q.n_tree > 1) {
+        uint32_t stack[96];
+        int sp = 0;
+        uint32_t node = 0;
+        while (true) {
+            const float4 *nd = a.q.nodes + (size_t)node * 4;
+            float4 lmin = nd[0], lmax = nd[1], rmin = nd[2], rmax = nd[3];
+            uint32_t child[2] = { __float_as_uint(lmin.w), __float_as_uint(rmin.w) };
+            uint32_t srange[2] = { __float_as_uint(lmax.w), __float_as_uint(rmax.w) };
+            bool hit[2];
+            hit[0] = a.q.space >= (srange[0] & 0xffffu) && a.q.space <= (srange[0] >> 16) && p.x >= lmin.x - grow && p.y >= lmin.y - grow &&
+                     p.z >= lmin.z - grow && p.x <= lmax.x + grow && p.y <= lmax.y + grow && p.z <= lmax.z + grow;
+            hit[1] = a.q.space >= (srange[1] & 0xffffu) && a.q.space <= (srange[1] >> 16) && p.x >= rmin.x - grow && p.y >= rmin.y - grow &&
+                     p.z >= rmin.z - grow && p.x <= rmax.x + grow && p.y <= rmax.y + grow && p.z <= rmax.z + grow;
+#pragma unroll
+            for (int side = 0; side < 2; side++) {
+                if (hit[side] && (child[side] & Q_LEAF_BIT)) q_point_candidate(a, __float_as_uint(a.q.leaf_min[child[side] & ~Q_LEAF_BIT].w), p, r, cc);
+            }
+            bool il = hit[0] && !(child[0] & Q_LEAF_BIT), ir = hit[1] && !(child[1] & Q_LEAF_BIT);
+            if (il) {
+                if (ir && sp < 96) stack[sp++] = child[1];
+                node = child[0];
+            } else if (ir) {
+                node = child[1];
+            } else {
+                if (sp == 0) break;
+                node = stack[--sp];
+            }
+        }
+    }
+    a.counts[r] = cc;
+}
+
+static void q_fill(bpc_context *ctx, QArgs &a, int space, int n, unsigned mask, int flags) {
+    a.n_rays = (uint32_t)n;
+    a.n_tree = ctx->n_tree;
+    a.space = (uint32_t)space;
+    a.mask = mask;
+    a.flags = (uint32_t)flags;
+    a.nodes = ctx->nodes.p;
+    a.leaf_min = ctx->leaf_min.p;
+    a.meta = ctx->meta.p;
+    a.xf = ctx->xf.p;
+    a.shape_xf = ctx->shape_xf.p;
+    a.shape_p = ctx->shape_p.p;
+    a.meshes = ctx->meshes.p;
+    a.mverts = ctx->mverts.p;
+    a.mplanes = ctx->mplanes.p;
+    a.mfaces = ctx->mfaces.p;
+    a.mindex = ctx->mindex.p;
+    a.big = ctx->big_items.p;
+    a.big_start = ctx->big_start.p;
+}
+
+extern "C" int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int max_results,
+                                          int32_t *out_counts, int32_t *out_bodies) {
+    if (!ctx) return -1;
+    if (space < 0 || (size_t)space >= ctx->spaces.size()) {
+        ctx->err = "bpc_space_intersect_points: no such space";
+        return -1;
+    }
+    if (n < 0 || max_results < 1 || max_results > 2048 || (n > 0 && (!points || !out_counts || !out_bodies))) {
+        ctx->err = "bpc_space_intersect_points: bad arguments";
+        return -1;
+    }
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (bpc_build_tree(ctx)) return -1;
+    size_t in_words = ((size_t)n * 3 + 3) & ~(size_t)3, cnt_words = ((size_t)n + 3) & ~(size_t)3, body_words = (size_t)n * max_results;
+    ctx->staging.reserve(in_words + cnt_words + body_words + 16, false, st);
+    if (!ctx->staging.p) {
+        ctx->err = "bpc_space_intersect_points: out of device memory";
+        return -1;
+    }
+    PArgs a;
+    q_fill(ctx, a.q, space, n, collision_mask, 0);
+    a.q.rays = ctx->staging.p;
+    a.q.out = nullptr;
+    a.max_results = (uint32_t)max_results;
+    a.counts = (int32_t *)(ctx->staging.p + in_words);
+    a.bodies = (int32_t *)(ctx->staging.p + in_words + cnt_words);
+    BPC_CHECK(cudaMemcpyAsync(ctx->staging.p, points, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+    BPC_CHECK(cudaMemsetAsync(a.bodies, 0xff, body_words * sizeof(int32_t), st));
+    k_intersect_points<<<(n + Q_THREADS - 1) / Q_THREADS, Q_THREADS, 0, st>>>(a);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaMemcpyAsync(out_counts, a.counts, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaMemcpyAsync(out_bodies, a.bodies, body_words * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}
+
 extern "C" int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *from_to, unsigned collision_mask, int flags,
                                         bpc_ray_result *out) {
     if (!ctx) return -1;
@@ -437,26 +567,9 @@ extern "C" int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, cons
     bpc_ray_result *d_out = (bpc_ray_result *)(ctx->staging.p + ((in_floats + 3) & ~(size_t)3));
     BPC_CHECK(cudaMemcpyAsync(d_in, from_to, in_floats * sizeof(float), cudaMemcpyHostToDevice, st));
     QArgs a;
-    a.n_rays = (uint32_t)n;
-    a.n_tree = ctx->n_tree;
-    a.space = (uint32_t)space;
+    q_fill(ctx, a, space, n, collision_mask, flags);
     a.rays = d_in;
     a.out = d_out;
-    a.mask = collision_mask;
-    a.flags = (uint32_t)flags;
-    a.nodes = ctx->nodes.p;
-    a.leaf_min = ctx->leaf_min.p;
-    a.meta = ctx->meta.p;
-    a.xf = ctx->xf.p;
-    a.shape_xf = ctx->shape_xf.p;
-    a.shape_p = ctx->shape_p.p;
-    a.meshes = ctx->meshes.p;
-    a.mverts = ctx->mverts.p;
-    a.mplanes = ctx->mplanes.p;
-    a.mfaces = ctx->mfaces.p;
-    a.mindex = ctx->mindex.p;
-    a.big = ctx->big_items.p;
-    a.big_start = ctx->big_start.p;
     k_intersect_rays<<<(n + Q_THREADS - 1) / Q_THREADS, Q_THREADS, 0, st>>>(a);
     BPC_CHECK(cudaGetLastError());
     BPC_CHECK(cudaMemcpyAsync(out, d_out, (size_t)n * sizeof(bpc_ray_result), cudaMemcpyDeviceToHost, st));

@@ -188,6 +188,33 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 	return hits;
 }
 
+int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) {
+	ERR_FAIL_NULL_V(server, 0);
+	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas, 0, "BradotPhysicsCUDA: intersect_point with exclude lists or areas is not supported yet.");
+	if (p_result_max <= 0 || !p_parameters.collide_with_bodies) {
+		return 0;
+	}
+	server->_flush_pending();
+	int max_r = p_result_max > 2048 ? 2048 : p_result_max;
+	float p[3] = { (float)p_parameters.position.x, (float)p_parameters.position.y, (float)p_parameters.position.z };
+	int32_t count = 0;
+	LocalVector<int32_t> slots;
+	slots.resize(max_r);
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_points(server->ctx, space_handle, 1, p, p_parameters.collision_mask, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	int cc = 0;
+	for (int i = 0; i < count; i++) {
+		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size()) {
+			continue;
+		}
+		r_results[cc].rid = server->body_of_slot[slots[i]]->self;
+		r_results[cc].collider_id = ObjectID();
+		r_results[cc].collider = nullptr;
+		r_results[cc].shape = 0;
+		cc++;
+	}
+	return cc;
+}
+
 bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_parameters, RayResult &r_result) {
 	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.pick_ray, false,
 			"BradotPhysicsCUDA: intersect_ray with exclude lists, areas or pick_ray is not supported yet.");

@@ -148,6 +148,13 @@ typedef struct bpc_ray_result {
 int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *from_to, unsigned collision_mask, int flags,
                              bpc_ray_result *out);
 
+/* PhysicsDirectSpaceState3D::intersect_point (servers/physics_server_3d.h:188-203; implementation
+ * modules/bradot_physics_3d/bradot_space_3d.cpp:62-107), batched: for each of n points (xyz, host) the bodies whose shape
+ * holds it.  out_counts: n; out_bodies: n x max_results body slots, -1 padded.  When more than max_results bodies hold a
+ * point, which ones are listed follows this backend's tree order (the reference's follows its own BVH). */
+int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int max_results,
+                               int32_t *out_counts, int32_t *out_bodies);
+
 /* ---- utilities exposed for tests and tools */
 /* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */
 int bpc_sort_u64(bpc_context *ctx, const uint64_t *keys_in, uint64_t *keys_out, int n);

@@ -13,7 +13,8 @@
 //
 // usage: oracle_step <scene.bscn> [--steps N] [--dump out.bdmp] [--dump-from A] [--dump-every K] [--rays rays.bin]
 //   rays.bin: uint32 n, then n x (from xyz, to xyz) float32; every dumped step also holds "rays" (n,8): hit, body
-//   index, position xyz, normal xyz of PhysicsDirectSpaceState3D::intersect_ray in space 0 (mask 0xffffffff)
+//   index, position xyz, normal xyz of PhysicsDirectSpaceState3D::intersect_ray in space 0 (mask 0xffffffff), and
+//   "points" (n,9): count and up to 8 body indices of intersect_point at each ray's origin
 //                    [--threads T] [--warmup W] [--quiet]
 // Timing JSON goes to stdout (one line).
 
@@ -286,6 +287,21 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 		}
 	}
 	d.arr("rays", step, "f4", { (uint64_t)n, 8 }, out.data(), out.size() * 4);
+	// intersect_point (bradot_space_3d.cpp:62-107) at every ray's origin: count, then up to 8 body indices
+	std::vector<int32_t> pts(n * 9, -1);
+	for (size_t i = 0; i < n; i++) {
+		PhysicsDirectSpaceState3D::PointParameters pp;
+		pp.position = Vector3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]);
+		pp.collision_mask = 0xffffffffu;
+		PhysicsDirectSpaceState3D::ShapeResult sr[8];
+		int cc = ds ? ds->intersect_point(pp, sr, 8) : 0;
+		pts[i * 9] = cc;
+		for (int k = 0; k < cc; k++) {
+			auto it = rid_index.find(sr[k].rid);
+			pts[i * 9 + 1 + k] = it == rid_index.end() ? -1 : it->second;
+		}
+	}
+	d.arr("points", step, "i4", { (uint64_t)n, 9 }, pts.data(), pts.size() * 4);
 }
 
 static void dump_meshes(Dump &d, World &w) {

@@ -78,3 +78,29 @@ def test_intersect_rays_edge_cases():
 def parity_needed():
     if not parity.have_oracle():
         pytest.skip("oracle/_ref/oracle_step not built")
+
+
+def test_intersect_points_against_the_reference():
+    parity_needed()
+    sc = scenes.mixed_pile(5, half=3.5)
+    rng = np.random.default_rng(9)
+    n = 6000
+    pts = rng.uniform(-3.4, 3.4, (n, 3))
+    pts[:, 1] = rng.uniform(-0.5, 4.0, n)          # some below the floor plane: inside the world boundary
+    rays = np.concatenate([pts, pts + 1.0], 1).astype(np.float32)
+    _, dump = parity.run_oracle(sc, 60, dump_from=0, dump_every=1, rays=rays)
+    ps = parity.new_server(sc, dump)
+    inside = 0
+    for k in (1, 30, 59):
+        parity.load_state(ps, dump, k)
+        counts, bodies = ps.intersect_points(rays[:, 0:3], max_results=8)
+        ref = dump[("points", k)]
+        differ = 0
+        for i in range(n):
+            a = set(bodies[i, :counts[i]].tolist())
+            b = set(ref[i, 1:1 + ref[i, 0]].tolist())
+            differ += a != b
+            inside += len(b)
+        assert differ <= n // 1000, (k, differ)      # a point within rounding of a surface may flip
+    assert inside > 1000
+    ps.finish()
