@@ -71,6 +71,19 @@ def reduce_max_ms(ms, device="cuda"):
     return float(t.item())
 
 
+def reduce_process_info(stats, device="cuda"):
+    """get_process_info of the whole job: all-reduce(SUM) of (active_objects, collision_pairs, island_count) over the ranks
+    (reference: BradotPhysicsServer3D::step sums them over its spaces, bradot_physics_server_3d.cpp:1632-1648).  The only
+    collective besides the timing reduction, issued after the timed region."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([stats["active_objects"], stats["collision_pairs"], stats["island_count"]], dtype=torch.int64, device=device)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    a, c, i = (int(v) for v in t.tolist())
+    return {"active_objects": a, "collision_pairs": c, "island_count": i}
+
+
 def reduce_sum(x, device="cuda"):
     import torch
     import torch.distributed as dist
@@ -204,6 +217,7 @@ def cuda_arm(args):
         acc["launches"] += st["kernel_launches"]
     barrier()
     ms = sum(a.elapsed_time(b) for a, b in ev)
+    process_info = reduce_process_info(st)
     stage_ms, stage_steps = ps.stage_times()
     ps.set_profiling(False)
     sampler.stop_flag = True
@@ -277,6 +291,7 @@ def cuda_arm(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(forces.nbytes), "d2h_bytes_per_step": int(nb * 12 * 4),
                     "checksum": checksum},
             "gpu_launches": acc["launches"],
+            "process_info": process_info,
             "clocks": sampler.summary(),
             "roofline": {"bound": "hbm", "kernel": "k_solve (pre-solve + %d Gauss-Seidel sweeps, cooperative launch)" % iters,
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,

@@ -106,8 +106,9 @@ r, w = dist.get_rank(), dist.get_world_size()
 lo, hi = bench.shard_range(10, r, w)
 ms = bench.reduce_max_ms(float(100 + 50 * r), device="cpu")
 tot = bench.reduce_sum(float(hi - lo), device="cpu")
+info = bench.reduce_process_info({"active_objects": 10 + r, "collision_pairs": 100 * (r + 1), "island_count": 3}, device="cpu")
 if r == 0:
-    print("RESULT", ms, tot)
+    print("RESULT", ms, tot, info["active_objects"], info["collision_pairs"], info["island_count"])
 dist.destroy_process_group()
 """
 
@@ -121,6 +122,7 @@ def test_gloo_two_ranks_timing_reduction(tmp_path):
     line = [l for l in r.stdout.splitlines() if l.startswith("RESULT")][0].split()
     assert float(line[1]) == 150.0    # max over ranks
     assert float(line[2]) == 10.0     # all units accounted for once
+    assert [int(x) for x in line[3:6]] == [21, 300, 6]   # get_process_info summed over the ranks
 
 
 def test_hull_builder_matches_the_reference_hull_topology():
