@@ -355,3 +355,23 @@ def free_fall(n=64, seed=3):
     sc.bodies["linvel"][first:] = rng.uniform(-2, 2, (n, 3)).astype(np.float32)
     sc.bodies["angvel"][first:] = rng.uniform(-3, 3, (n, 3)).astype(np.float32)
     return sc
+
+
+def sleepers(n_boxes=6):
+    """Sleep / wake test: separate boxes dropped from small heights (each its own island, asleep one after the other),
+    a two-box stack, and a sphere released from high up that lands on a sleeping box and wakes its island."""
+    sc = Scene(name="sleepers")
+    sc.add_static_plane((0, 1, 0), 0.0)
+    box = sc.add_shape(SHAPE_BOX, (0.4, 0.4, 0.4, 0))
+    ball = sc.add_shape(SHAPE_SPHERE, (0.3, 0, 0, 0))
+    xf = np.tile(IDENT12, (n_boxes, 1))
+    xf[:, 9] = (np.arange(n_boxes) - (n_boxes - 1) * 0.5) * 2.0
+    xf[:, 10] = 0.41 + 0.05 * np.arange(n_boxes)
+    sc.add_bodies(n_boxes, shape=box, xf=xf, mass=1.0)
+    top = IDENT12.copy()
+    top[9], top[10] = xf[0, 9], 1.25          # second box resting on box 0
+    sc.add_bodies(1, shape=box, xf=top, mass=1.0)
+    hi = IDENT12.copy()
+    hi[9], hi[10] = xf[2, 9] + 0.05, 14.0     # lands on box 2 after ~100 steps, when it is asleep
+    sc.add_bodies(1, shape=ball, xf=hi, mass=2.0)
+    return sc

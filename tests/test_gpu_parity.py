@@ -121,6 +121,42 @@ def test_free_run_energy_and_momentum_600_steps(name, tol):
     ps.finish()
 
 
+def test_sleep_and_wake_follow_the_reference_step_by_step():
+    """a17 (sleep_test / _check_suspend, all-or-nothing per island, a hit wakes the island): separate boxes fall asleep one
+    after the other (steps 37-44 in the reference), a ball lands on a sleeping box at step 100 and wakes it, both sleep
+    again at 130.  Teacher-forced: active flags and still times after every single step equal the reference's."""
+    _need_oracle()
+    sc = scenes.sleepers()
+    steps = 200
+    _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1)
+    ref_act = np.array([dump[("bodies", k)][:, 18] for k in range(0, steps + 1)])
+    assert (np.diff(ref_act, axis=0) < 0).sum() >= 8 and (np.diff(ref_act, axis=0) > 0).sum() >= 1   # the scene does sleep and wake
+    ps = parity.new_server(sc, dump)
+    for k in range(1, steps):
+        parity.load_state(ps, dump, k)
+        ps.set_solve_order(parity.solve_order(dump, k + 1))
+        ps.step(sc.dt)
+        act = ps.bodies_read(server.FIELD_ACTIVE)[:, 0]
+        still = ps.bodies_read(server.FIELD_STILL_TIME)[:, 0]
+        ref = dump[("bodies", k + 1)]
+        assert np.array_equal(act > 0, ref[:, 18] > 0), (k + 1, act, ref[:, 18])
+        dyn = sc.bodies["mode"] >= scenes.MODE_RIGID
+        assert np.max(np.abs(still[dyn] - ref[dyn, 19])) <= 1e-6, (k + 1, still, ref[:, 19])
+    ps.finish()
+    # free-running (our own sweep order): the same bodies sleep and wake, within two steps of the reference
+    ps = parity.new_server(sc, dump)
+    gpu_act = [dump[("bodies", 0)][:, 18] > 0]
+    for k in range(steps):
+        ps.step(sc.dt)
+        gpu_act.append(ps.bodies_read(server.FIELD_ACTIVE)[:, 0] > 0)
+    ps.finish()
+    gpu_act = np.array(gpu_act)
+    for b in range(1, len(sc.bodies)):
+        rc = np.nonzero(np.diff(ref_act[:, b]))[0]
+        gc = np.nonzero(np.diff(gpu_act[:, b].astype(np.int8)))[0]
+        assert len(rc) == len(gc) and np.all(np.abs(rc - gc) <= 2), (b, rc, gc)
+
+
 def test_teacher_forced_joint_chains():     # pin + hinge chains of convex hulls (C4 layout), linked bodies excepted from colliding
     _need_oracle()
     sc = scenes.convex_chains(n_chains=9, chain_len=5, n_hulls=4)
