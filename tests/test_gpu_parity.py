@@ -157,6 +157,23 @@ def test_sleep_and_wake_follow_the_reference_step_by_step():
         assert len(rc) == len(gc) and np.all(np.abs(rc - gc) <= 2), (b, rc, gc)
 
 
+@pytest.mark.parametrize("name", ["sleepers", "mixed"])
+def test_process_info_matches_the_reference(name):
+    """a18: get_process_info (active objects, collision pairs, island count) after each teacher-forced step."""
+    _need_oracle()
+    sc = scenes.sleepers() if name == "sleepers" else scenes.mixed_pile(4, half=3.0)
+    steps = 120
+    _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1)
+    ps = parity.new_server(sc, dump)
+    for k in list(range(1, 60, 3)) + list(range(60, steps - 1, 7)):
+        parity.load_state(ps, dump, k)
+        ps.step(sc.dt)
+        st = ps.stats()
+        ref = dump[("stats", k + 1)]    # island_count, active_objects, collision_pairs
+        assert (st["island_count"], st["active_objects"], st["collision_pairs"]) == (int(ref[0]), int(ref[1]), int(ref[2])), (k + 1, st, ref)
+    ps.finish()
+
+
 def test_teacher_forced_joint_chains():     # pin + hinge chains of convex hulls (C4 layout), linked bodies excepted from colliding
     _need_oracle()
     sc = scenes.convex_chains(n_chains=9, chain_len=5, n_hulls=4)
