@@ -157,6 +157,32 @@ def test_sleep_and_wake_follow_the_reference_step_by_step():
         assert len(rc) == len(gc) and np.all(np.abs(rc - gc) <= 2), (b, rc, gc)
 
 
+@pytest.mark.parametrize("name", ["mixed", "convex"])
+def test_mass_properties_match_the_reference(name):
+    """a1 (update_mass_properties: volume-weighted centre of mass, inertia tensor, Jacobi diagonalisation): what
+    bpc_bodies_create derives on its own against what the reference derived for the same scene.  (The other parity
+    tests import the reference's mass data, so that a difference here cannot hide behind them or blur them.)"""
+    _need_oracle()
+    sc = scenes.mixed_pile(4, half=3.0) if name == "mixed" else scenes.convex_pile(3)
+    _, dump = parity.run_oracle(sc, 1, dump_from=0, dump_every=1)
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc, server.meshes_from_dump(dump))   # hull topology from the reference, mass data our own
+    mine = ps.bodies_read(server.FIELD_MASS_PROPS)
+    ps.finish()
+    ref = dump[("mass_props", -1)]
+    dyn = sc.bodies["mode"] >= scenes.MODE_RIGID
+    assert dyn.sum() > 20
+    assert parity.rel_err(mine[dyn, 0], ref[dyn, 0], 1e-6) < 1e-6          # inverse mass
+    assert parity.rel_err(mine[dyn, 1:4], ref[dyn, 1:4], 1e-3) < 1e-4      # inverse principal inertia
+    assert np.max(np.abs(mine[dyn, 4:7] - ref[dyn, 4:7])) < 1e-6           # centre of mass (local)
+    # principal axes: same frame up to the sign of each axis (columns), as any eigenvector routine
+    a = mine[dyn, 7:16].reshape(-1, 3, 3)
+    b = ref[dyn, 7:16].reshape(-1, 3, 3)
+    same = np.abs(np.einsum("nij,nij->nj", a, b))                          # |column_j(a) . column_j(b)|
+    iso = np.abs(ref[dyn, 1:2] - ref[dyn, 3:4]) < 1e-5 * np.abs(ref[dyn, 1:2])   # spheres / cubes: any frame is principal
+    assert np.all((same > 1 - 1e-4) | iso), float(same[~iso[:, 0]].min())
+
+
 @pytest.mark.parametrize("name", ["sleepers", "mixed"])
 def test_process_info_matches_the_reference(name):
     """a18: get_process_info (active objects, collision pairs, island count) after each teacher-forced step."""
