@@ -121,7 +121,7 @@ def teacher_forced(sc, steps, check_steps, import_order=True, dump=None):
     if dump is None:
         _, dump = run_oracle(sc, steps, dump_from=0, dump_every=1)
     ps = new_server(sc, dump)
-    worst = {"contact": 0.0, "state": 0.0, "pairs": 0, "colliding": 0, "contacts": 0}
+    worst = {"contact": 0.0, "state": 0.0, "pairs": 0, "colliding": 0, "contacts": 0, "items": 0.0, "item_pairs_differ": 0}
     for k in check_steps:
         assert k >= 1
         load_state(ps, dump, k)
@@ -155,6 +155,13 @@ def teacher_forced(sc, steps, check_steps, import_order=True, dump=None):
             av = ps.bodies_read(server.FIELD_ANGULAR_VELOCITY)
             e = max(rel_err(xf, ref[:, 0:12], 1.0), rel_err(lv, ref[:, 12:15], 1.0), rel_err(av, ref[:, 15:18], 1.0))
             worst["state"] = max(worst["state"], e)
+            # broadphase items after the step (a3 / a4): exact shape AABB with its 5 % growth, the stored hysteretic box,
+            # the pair count that steers the next margin
+            it = ps.bodies_read(server.FIELD_ITEM_BOX)
+            rit = dump[("items", k + 1)]
+            moved = sc.bodies["mode"] >= scenes.MODE_RIGID
+            worst["items"] = max(worst["items"], rel_err(it[moved, 0:12], rit[moved, 0:12], 1.0))
+            worst["item_pairs_differ"] += int((it[moved, 12] != rit[moved, 12]).sum())
     ps.finish()
     return worst
 

@@ -47,6 +47,7 @@ def _check(w):
     assert w["colliding"] > 0 and w["contacts"] > 0, "scene never produced contacts: %r" % w
     assert w["contact"] < CONTACT_TOL, w
     assert w["state"] < STATE_TOL, w
+    assert w["items"] < 1e-5 and w["item_pairs_differ"] == 0, w   # exact AABB, stored (hysteretic) box, pair count per item
 
 
 def test_teacher_forced_pyramid():          # box-box, box-plane
