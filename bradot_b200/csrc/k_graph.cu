@@ -66,21 +66,10 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_union_runs(uint32_t n, const 
     if (a >= n) return;
     uint32_t k = a_begin[a], ke = a_end[a];
     if (k >= ke || (meta[a].x & 0xffu) == MODE_STATIC) return;
-    uint32_t ra = cc_find(label, a); // kept across the run: one find per pair instead of two
-    for (; k < ke; k++) {
+    for (; k < ke; k++) { // (keeping a's root across the run was measured slower: stale roots cost more CAS retries than the finds saved)
         uint32_t b = (uint32_t)keys[k];
         if ((meta[b].x & 0xffu) == MODE_STATIC) continue;
-        uint32_t rb = cc_find(label, b);
-        while (ra != rb) {
-            uint32_t hi = max(ra, rb), lo = min(ra, rb);
-            uint32_t old = atomicCAS(&label[hi], hi, lo);
-            if (old == hi) {
-                ra = lo;
-                break;
-            }
-            ra = cc_find(label, ra); // someone hooked one of the roots meanwhile
-            rb = cc_find(label, rb);
-        }
+        cc_union(label, a, b);
     }
 }
 

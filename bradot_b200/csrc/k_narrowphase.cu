@@ -127,7 +127,11 @@ __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
             bool collide_A = (mode_a > MODE_KINEMATIC) && (mb.y & ma.z);
             bool collide_B = (mode_b > MODE_KINEMATIC) && (ma.y & mb.z);
             uint32_t nb = count; // collided = false, contacts untouched
-            if (interacts && !excepted && (collide_A || collide_B)) {
+            bool both_hulls = (ma.x >> 24) == SH_CONVEX && (mb.x >> 24) == SH_CONVEX;
+            if (interacts && !excepted && (collide_A || collide_B) && count > 0 && !both_hulls) {
+                // cached contacts have to be validated by the full pass whatever this one would decide: do not decide twice
+                work = true;
+            } else if (interacts && !excepted && (collide_A || collide_B)) {
                 BodyXf bxa = a.xf[ia], bxb = a.xf[ib];
                 M3 bA(f4v(bxa.r0), f4v(bxa.r1), f4v(bxa.r2)), bB(f4v(bxb.r0), f4v(bxb.r1), f4v(bxb.r2));
                 V3 offset_B = f4v(bxb.o) - f4v(bxa.o);
@@ -137,14 +141,16 @@ __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
                 Sh sb = load_shape_fast(a, ib, mb.x);
                 V3 sep_axis = f4v(h.sep);
                 nb |= (collide_A ? 0x200u : 0u) | (collide_B ? 0x400u : 0u);
-                if (sa.type == SH_CONVEX && sb.type == SH_CONVEX && cw_fits(sa.m) && cw_fits(sb.m)) {
+                bool hulls = both_hulls && cw_fits(sa.m) && cw_fits(sb.m);
+                if (count > 0) {
+                    work = !hulls;
+                    cwork = hulls;
+                } else if (hulls) {
                     // three likely separating axes here; whatever they do not settle goes to the warp-per-pair kernel
-                    cwork = !cw_quick_separated(sa, xA, sb, xB, sep_axis) || count > 0;
+                    cwork = !cw_quick_separated(sa, xA, sb, xB, sep_axis);
                 } else {
                     Manifold *none = nullptr;
-                    bool collided = solve_static<true>(sa, xA, sb, xB, *none, &sep_axis);
-                    // the full pass decides again and generates contacts; cached contacts must be validated even when apart
-                    work = collided || count > 0;
+                    work = solve_static<true>(sa, xA, sb, xB, *none, &sep_axis);
                 }
             }
             if (!work && !cwork) {
