@@ -183,7 +183,6 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
         if (descs[i].space >= ctx->spaces.size()) return fail(ctx, "bpc_bodies_create: invalid space");
         if (descs[i].shape >= ctx->h_shapes.size()) return fail(ctx, "bpc_bodies_create: invalid shape");
         if (descs[i].mode > MODE_RIGID_LINEAR) return fail(ctx, "bpc_bodies_create: invalid body mode");
-        if (descs[i].mode == MODE_KINEMATIC) return fail(ctx, "bpc_bodies_create: kinematic bodies are not supported yet");
     }
     if (!grow(ctx, ctx->xf, total) || !grow(ctx, ctx->shape_xf, total) || !grow(ctx, ctx->vel, total) || !grow(ctx, ctx->massw, total) ||
         !grow(ctx, ctx->props, total) || !grow(ctx, ctx->forces, total) || !grow(ctx, ctx->meta, total) || !grow(ctx, ctx->shape_id, total) ||
@@ -214,7 +213,14 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
         memset(&mw[i], 0, sizeof(BodyMassW));
         mw[i].m = make_float4(inv_mass, d.friction, d.bounce, 0.f);
         uint32_t flags = (d.flags & 1u ? BF_CAN_SLEEP : 0u) | (d.flags & 4u ? 0u : BF_ACTIVE);
-        if (d.mode == MODE_STATIC) flags &= ~BF_ACTIVE;
+        // a kinematic body is inactive until it is given somewhere to go (set_mode: bradot_body_3d.cpp:218-231), and its
+        // velocities are whatever its moves imply
+        if (d.mode == MODE_STATIC || d.mode == MODE_KINEMATIC) flags &= ~BF_ACTIVE;
+        if (d.mode == MODE_KINEMATIC) {
+            vel[i].lin = make_float4(0.f, 0.f, 0.f, 0.f);
+            vel[i].ang = make_float4(0.f, 0.f, 0.f, 0.f);
+            ctx->h_kin_ids.push_back(first + i);
+        }
         bool ident = true;
         for (int q = 0; q < 12; q++) ident = ident && d.shape_xf[q] == ((q == 0 || q == 4 || q == 8) ? 1.f : 0.f);
         if (ident) flags |= BF_SHAPE_IDENT;
@@ -240,6 +246,21 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
     BPC_CHECK(cudaMemsetAsync(ctx->items.p + first, 0, n * sizeof(ItemBox), st));
     BPC_CHECK(cudaMemsetAsync(ctx->npairs.p + first, 0, n * sizeof(uint32_t), st));
     ctx->n_bodies = (uint32_t)total;
+    if (!ctx->h_kin_ids.empty()) {
+        ctx->kin.reserve(total, true, st);
+        ctx->kin_ids.reserve(ctx->h_kin_ids.size(), false, st);
+        if (!ctx->kin.p || !ctx->kin_ids.p || ctx->kin.cap < total) return fail(ctx, "bpc_bodies_create: out of device memory");
+        BPC_CHECK(cudaMemcpyAsync(ctx->kin_ids.p, ctx->h_kin_ids.data(), ctx->h_kin_ids.size() * 4, cudaMemcpyHostToDevice, st));
+        for (int i = 0; i < n; i++) {
+            if (descs[i].mode != MODE_KINEMATIC) continue;
+            KinState k;
+            k.target = xf[i];
+            k.clin = make_float4(descs[i].linvel[0], descs[i].linvel[1], descs[i].linvel[2], 0.f);
+            k.cang = make_float4(descs[i].angvel[0], descs[i].angvel[1], descs[i].angvel[2], 0.f);
+            BPC_CHECK(cudaMemcpyAsync(ctx->kin.p + first + i, &k, sizeof(KinState), cudaMemcpyHostToDevice, st));
+            BPC_CHECK(cudaStreamSynchronize(st)); // k is a stack temporary
+        }
+    }
     // two shape-update passes, as the engine does: creation, then the pending-shape flush at the
     // start of the first step (P3D/bradot_physics_server_3d.cpp:1728-1733)
     if (bpc_launch_refresh_bodies(ctx, first, (uint32_t)n, 2)) return -1;
@@ -308,6 +329,8 @@ static int field_width(int field) {
         case BPC_FIELD_LINEAR_VELOCITY: case BPC_FIELD_ANGULAR_VELOCITY: return 3;
         case BPC_FIELD_ACTIVE: case BPC_FIELD_STILL_TIME: return 1;
         case BPC_FIELD_MASS_PROPS: return 16;
+        case BPC_FIELD_KINEMATIC_TARGET: return 12;
+        case BPC_FIELD_KINEMATIC_VELOCITY: return 6;
         case BPC_FIELD_ITEM_BOX: return 14;
         case BPC_FIELD_APPLIED_FORCE: return 6;
         default: return 0;
@@ -408,7 +431,35 @@ extern "C" int bpc_bodies_write(bpc_context *ctx, int field, int first, int n, c
             std::vector<BodyXf> h(n);
             for (int i = 0; i < n; i++) h[i] = pack_xf(in + 12 * i);
             if (store(ctx, h, ctx->xf, first)) return -1;
+            for (int i = 0; i < n; i++) { // placing a kinematic body: it is there, and there is where it wants to be
+                if (ctx->h_mode[first + i] != MODE_KINEMATIC) continue;
+                BPC_CHECK(cudaMemcpyAsync(&ctx->kin.p[first + i].target, &h[i], sizeof(BodyXf), cudaMemcpyHostToDevice, ctx->stream));
+            }
+            BPC_CHECK(cudaStreamSynchronize(ctx->stream));
             refresh = true;
+        } break;
+        case BPC_FIELD_KINEMATIC_TARGET:
+        case BPC_FIELD_KINEMATIC_VELOCITY: {
+            std::vector<uint4> meta;
+            bool any = false;
+            if (field == BPC_FIELD_KINEMATIC_TARGET && fetch(ctx, meta, ctx->meta, first, n)) return -1;
+            std::vector<BodyXf> keep(n);
+            std::vector<float4> cv((size_t)n * 2);
+            for (int i = 0; i < n; i++) {
+                if (ctx->h_mode[first + i] != MODE_KINEMATIC) continue;
+                any = true;
+                if (field == BPC_FIELD_KINEMATIC_TARGET) {
+                    keep[i] = pack_xf(in + 12 * i);
+                    BPC_CHECK(cudaMemcpyAsync(&ctx->kin.p[first + i].target, &keep[i], sizeof(BodyXf), cudaMemcpyHostToDevice, ctx->stream));
+                    meta[i].x |= (BF_ACTIVE << 8); // set_active(true), bradot_body_3d.cpp:358
+                } else {
+                    cv[2 * i] = make_float4(in[6 * i], in[6 * i + 1], in[6 * i + 2], 0.f);
+                    cv[2 * i + 1] = make_float4(in[6 * i + 3], in[6 * i + 4], in[6 * i + 5], 0.f);
+                    BPC_CHECK(cudaMemcpyAsync(&ctx->kin.p[first + i].clin, &cv[2 * i], 2 * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+                }
+            }
+            if (any && field == BPC_FIELD_KINEMATIC_TARGET && store(ctx, meta, ctx->meta, first)) return -1;
+            BPC_CHECK(cudaStreamSynchronize(ctx->stream));
         } break;
         case BPC_FIELD_LINEAR_VELOCITY:
         case BPC_FIELD_ANGULAR_VELOCITY: {

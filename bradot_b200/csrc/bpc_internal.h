@@ -122,6 +122,12 @@ struct Stats {
     int active_objects, collision_pairs, island_count, contact_pairs, colors, contacts, overflow, steps;
 };
 
+// Kinematic bodies only: where the host wants the body after the next step, and its constant velocities.
+struct KinState {
+    BodyXf target;
+    float4 clin, cang;
+};
+
 struct bpc_context {
     int device = 0;
     cudaStream_t stream = 0;
@@ -165,6 +171,9 @@ struct bpc_context {
     DevBuf<float4> shape_p;    // per-body copy of the shape parameters (convex: x = mesh index bits)
     DevBuf<ItemBox> items;
     DevBuf<uint32_t> npairs;   // pairs per item after the last broadphase update (drives the margin)
+    DevBuf<KinState> kin;        // indexed by body; allocated when the first kinematic body is created
+    DevBuf<uint32_t> kin_ids;    // the kinematic bodies
+    std::vector<uint32_t> h_kin_ids;
     DevBuf<uint32_t> tree_items; // body ids that live in the LBVH (everything except unbounded statics)
     uint32_t n_tree = 0;
     DevBuf<uint32_t> island; // connected-component label per body

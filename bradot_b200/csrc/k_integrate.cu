@@ -83,6 +83,8 @@ __device__ __forceinline__ void transform_dependent(const M3 &B, const BodyProps
     mw.i2 = v4(iinv.r[2], com.z);
 }
 
+__device__ __forceinline__ void store_item_box(const Box3 &box, ItemBox &it, int np, bool init);
+
 // Shape AABB + stored broadphase box.  `init` = item creation: the stored box is the exact one
 // (core/math/bvh_public.inc:2-20 "we do not expand the AABB for the first create").
 __device__ __forceinline__ void update_item(const X3 &body, const BodyXf &sx, const ShapeRec &sh, ItemBox &it, int np, bool init) {
@@ -97,6 +99,11 @@ __device__ __forceinline__ void update_item(const X3 &body, const BodyXf &sx, co
     box = grow_by(box, g);
     it.cache_pos = v4(box.pos, 0.f);
     it.cache_size = v4(box.size, 0.f);
+    store_item_box(box, it, np, init);
+}
+
+// BVH_Manager::move with the item_move hysteresis; `init` = create (the exact box is stored)
+__device__ __forceinline__ void store_item_box(const Box3 &box, ItemBox &it, int np, bool init) {
     V3 bmin = box.pos, bmax = box.pos + box.size;
     if (init) {
         it.smin = v4(bmin, 0.f);
@@ -185,6 +192,107 @@ __global__ void __launch_bounds__(IT_THREADS) k_integrate_velocities(uint32_t n,
     items[i] = it;
 }
 
+// ---- kinematic bodies --------------------------------------------------------------------------
+// Basis::get_axis_angle (core/math/basis.cpp:760-836)
+__device__ inline void basis_axis_angle(const M3 &m, V3 &axis, float &angle) {
+    const float eps = (float)BPC_CMP_EPSILON;
+    float x, y, z;
+    if (is_zero_approx(m.r[0].y - m.r[1].x) && is_zero_approx(m.r[0].z - m.r[2].x) && is_zero_approx(m.r[1].z - m.r[2].y)) {
+        bool diagonal = is_zero_approx(m.r[0].y) && is_zero_approx(m.r[0].z) && is_zero_approx(m.r[1].x) && is_zero_approx(m.r[1].z) &&
+                        is_zero_approx(m.r[2].x) && is_zero_approx(m.r[2].y);
+        if (diagonal && ((double)fabsf(m.r[0].x + m.r[1].y + m.r[2].z - 3) < 3 * BPC_CMP_EPSILON)) {
+            axis = V3(0.f, 1.f, 0.f);
+            angle = 0.f;
+            return;
+        }
+        float xx = (m.r[0].x + 1) / 2, yy = (m.r[1].y + 1) / 2, zz = (m.r[2].z + 1) / 2;
+        float xy = (m.r[0].y + m.r[1].x) / 4, xz = (m.r[0].z + m.r[2].x) / 4, yz = (m.r[1].z + m.r[2].y) / 4;
+        const float sqrt12 = (float)0.7071067811865475244008443621048490;
+        if ((xx > yy) && (xx > zz)) {
+            if (xx < eps) { x = 0; y = sqrt12; z = sqrt12; }
+            else { x = sqrtf(xx); y = xy / x; z = xz / x; }
+        } else if (yy > zz) {
+            if (yy < eps) { x = sqrt12; y = 0; z = sqrt12; }
+            else { y = sqrtf(yy); x = xy / y; z = yz / y; }
+        } else {
+            if (zz < eps) { x = sqrt12; y = sqrt12; z = 0; }
+            else { z = sqrtf(zz); x = xz / z; y = yz / z; }
+        }
+        axis = V3(x, y, z);
+        angle = (float)3.14159265358979323846;
+        return;
+    }
+    float a = m.r[2].y - m.r[1].z, b = m.r[0].z - m.r[2].x, c = m.r[1].x - m.r[0].y;
+    double s = (double)sqrtf(a * a + b * b + c * c);
+    if (fabs(s) < BPC_CMP_EPSILON) s = 1;
+    axis = V3((float)((double)a / s), (float)((double)b / s), (float)((double)c / s));
+    float cs = (m.r[0].x + m.r[1].y + m.r[2].z - 1) / 2;
+    // Math::acos clamps.  Evaluated in double and rounded: near cs = 1 (a small turn per step) the last bit of the angle decides
+    // contacts' friction branches a step later, and CUDA's acosf is 1 ulp, not correctly rounded like the host's
+    angle = cs < -1.f ? (float)3.14159265358979323846 : (cs > 1.f ? 0.f : (float)acos((double)cs));
+}
+
+// integrate_forces of an active kinematic body (bradot_body_3d.cpp:611-627, 665-667): velocities from the move the host
+// asked for, and the broadphase box swept along the move (_update_shapes_with_motion, bradot_collision_object_3d.cpp:186-211)
+__global__ void __launch_bounds__(IT_THREADS) k_kinematic_forces(uint32_t n_kin, const uint32_t *__restrict__ ids, float dt, const BodyXf *__restrict__ xf,
+                                                                 const KinState *__restrict__ kin, BodyVel *__restrict__ vel, const uint4 *__restrict__ meta,
+                                                                 const BodyXf *__restrict__ shape_xf, const uint32_t *__restrict__ shape_id,
+                                                                 const ShapeRec *__restrict__ shapes, ItemBox *__restrict__ items,
+                                                                 const uint32_t *__restrict__ npairs) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_kin) return;
+    uint32_t i = ids[t];
+    if (!((meta[i].x >> 8) & BF_ACTIVE)) return;
+    BodyXf x = xf[i];
+    KinState k = kin[i];
+    V3 motion = f4v(k.target.o) - f4v(x.o);
+    V3 lin = f4v(k.clin) + motion / dt;
+    M3 rot = orthonormalized(load_basis(k.target)) * transposed(orthonormalized(load_basis(x)));
+    V3 axis;
+    float angle;
+    basis_axis_angle(rot, axis, angle);
+    axis = normalized(axis);
+    V3 ang = f4v(k.cang) + axis * (angle / dt);
+    vel[i].lin = v4(lin, 0.f);
+    vel[i].ang = v4(ang, 0.f);
+    BodyXf sx = shape_xf[i];
+    X3 X = X3(load_basis(x), f4v(x.o)) * X3(load_basis(sx), f4v(sx.o));
+    const ShapeRec sh = shapes[shape_id[i]];
+    Box3 la;
+    la.pos = f4v(sh.aabb_pos);
+    la.size = f4v(sh.aabb_size);
+    Box3 box = xform_aabb(X, la);
+    // AABB::merge_with the same box moved by `motion` (core/math/aabb.cpp:49-74)
+    V3 beg_1 = box.pos, beg_2 = box.pos + motion, end_1 = box.size + beg_1, end_2 = box.size + beg_2;
+    V3 mn(beg_1.x < beg_2.x ? beg_1.x : beg_2.x, beg_1.y < beg_2.y ? beg_1.y : beg_2.y, beg_1.z < beg_2.z ? beg_1.z : beg_2.z);
+    V3 mx(end_1.x > end_2.x ? end_1.x : end_2.x, end_1.y > end_2.y ? end_1.y : end_2.y, end_1.z > end_2.z ? end_1.z : end_2.z);
+    box.pos = mn;
+    box.size = mx - mn;
+    ItemBox it = items[i];
+    it.cache_pos = v4(box.pos, 0.f);
+    it.cache_size = v4(box.size, 0.f);
+    store_item_box(box, it, (int)npairs[i], false);
+    items[i] = it;
+}
+
+// integrate_velocities of an active kinematic body (bradot_body_3d.cpp:700-708): it is where it was told to be; a body
+// that did not move goes back to sleep
+__global__ void __launch_bounds__(IT_THREADS) k_kinematic_velocities(uint32_t n_kin, const uint32_t *__restrict__ ids, BodyXf *__restrict__ xf,
+                                                                     const KinState *__restrict__ kin, const BodyVel *__restrict__ vel,
+                                                                     uint4 *__restrict__ meta) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_kin) return;
+    uint32_t i = ids[t];
+    uint4 mt = meta[i];
+    if (!((mt.x >> 8) & BF_ACTIVE)) return;
+    xf[i] = kin[i].target;
+    BodyVel v = vel[i];
+    if (f4v(v.lin) == V3() && f4v(v.ang) == V3()) { // no contact reporting yet: contacts.size() == 0
+        mt.x &= ~(BF_ACTIVE << 8);
+        meta[i] = mt;
+    }
+}
+
 // Body creation / teleport: derive world mass data and the broadphase item from the transform.
 __global__ void __launch_bounds__(IT_THREADS) k_refresh_bodies(uint32_t first, uint32_t n, int pass, const BodyXf *__restrict__ xf,
                                                                BodyMassW *__restrict__ massw, const BodyProps *__restrict__ props,
@@ -265,6 +373,12 @@ int bpc_launch_integrate_forces(bpc_context *ctx, float dt) {
     k_integrate_forces<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->vel.p, ctx->props.p, ctx->forces.p, ctx->massw.p,
                                                                             ctx->meta.p, ctx->d_spaces.p, ctx->counters.p);
     ctx->launches += 1;
+    uint32_t nk = (uint32_t)ctx->h_kin_ids.size();
+    if (nk) {
+        k_kinematic_forces<<<nblk(nk, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(nk, ctx->kin_ids.p, dt, ctx->xf.p, ctx->kin.p, ctx->vel.p, ctx->meta.p,
+                                                                                 ctx->shape_xf.p, ctx->shape_id.p, ctx->shapes.p, ctx->items.p, ctx->npairs.p);
+        ctx->launches += 1;
+    }
     BPC_CHECK(cudaGetLastError());
     return 0;
 }
@@ -272,6 +386,11 @@ int bpc_launch_integrate_forces(bpc_context *ctx, float dt) {
 int bpc_launch_integrate_velocities(bpc_context *ctx, float dt) {
     uint32_t n = ctx->n_bodies;
     if (!n) return 0;
+    uint32_t nk = (uint32_t)ctx->h_kin_ids.size();
+    if (nk) {
+        k_kinematic_velocities<<<nblk(nk, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(nk, ctx->kin_ids.p, ctx->xf.p, ctx->kin.p, ctx->vel.p, ctx->meta.p);
+        ctx->launches += 1;
+    }
     k_integrate_velocities<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->xf.p, ctx->vel.p, ctx->massw.p, ctx->props.p,
                                                                                 ctx->meta.p, ctx->shape_xf.p, ctx->shape_id.p,
                                                                                 ctx->shapes.p, ctx->items.p, ctx->npairs.p);

@@ -375,3 +375,27 @@ def sleepers(n_boxes=6):
     hi[9], hi[10] = xf[2, 9] + 0.05, 14.0     # lands on box 2 after ~100 steps, when it is asleep
     sc.add_bodies(1, shape=ball, xf=hi, mass=2.0)
     return sc
+
+
+def kinematic_platform():
+    """A kinematic platform (moved by body_set_state(TRANSFORM) every step: 0.6 m/s along x, 0.3 rad/s about y, scripted
+    through its scene velocities) carrying boxes and spheres over a ground plane; a second kinematic box stands still."""
+    sc = Scene(name="kinematic_platform")
+    sc.add_static_plane((0, 1, 0), 0.0)
+    slab = sc.add_shape(SHAPE_BOX, (2.0, 0.2, 2.0, 0))
+    box = sc.add_shape(SHAPE_BOX, (0.25, 0.25, 0.25, 0))
+    ball = sc.add_shape(SHAPE_SPHERE, (0.25, 0, 0, 0))
+    x = IDENT12.copy()
+    x[10] = 1.0
+    sc.add_bodies(1, mode=MODE_KINEMATIC, shape=slab, xf=x, linvel=(0.6, 0.0, 0.0), angvel=(0.0, 0.3, 0.0))
+    x2 = IDENT12.copy()
+    x2[9], x2[10] = 6.0, 0.5
+    sc.add_bodies(1, mode=MODE_KINEMATIC, shape=slab, xf=x2)   # never moved: stays inactive
+    g = np.stack(np.meshgrid(np.arange(3), np.arange(3), indexing="ij"), -1).reshape(-1, 2)
+    xf = np.tile(IDENT12, (9, 1))
+    xf[:, 9] = (g[:, 0] - 1) * 1.1
+    xf[:, 11] = (g[:, 1] - 1) * 1.1
+    xf[:, 10] = 1.5
+    shape = np.where(np.arange(9) % 2 == 0, box, ball).astype(np.uint32)
+    sc.add_bodies(9, shape=shape, xf=xf, mass=1.0)
+    return sc

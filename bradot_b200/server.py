@@ -21,7 +21,8 @@ LIB_PATH = os.environ.get("BPC_LIBRARY", os.path.join(_HERE, "libbradot_physics_
 
 FIELD_TRANSFORM, FIELD_LINEAR_VELOCITY, FIELD_ANGULAR_VELOCITY, FIELD_ACTIVE = 0, 1, 2, 3
 FIELD_MASS_PROPS, FIELD_ITEM_BOX, FIELD_APPLIED_FORCE, FIELD_STILL_TIME = 4, 5, 6, 7
-_FIELD_WIDTH = {0: 12, 1: 3, 2: 3, 3: 1, 4: 16, 5: 14, 6: 6, 7: 1}
+FIELD_KINEMATIC_TARGET, FIELD_KINEMATIC_VELOCITY = 8, 9   # write only, kinematic bodies
+_FIELD_WIDTH = {0: 12, 1: 3, 2: 3, 3: 1, 4: 16, 5: 14, 6: 6, 7: 1, 8: 12, 9: 6}
 
 SPACE_PARAM_CONTACT_RECYCLE_RADIUS, SPACE_PARAM_CONTACT_MAX_SEPARATION = 0, 1
 SPACE_PARAM_CONTACT_MAX_ALLOWED_PENETRATION, SPACE_PARAM_CONTACT_DEFAULT_BIAS = 2, 3
@@ -278,7 +279,13 @@ class PhysicsServerCUDA:
                 self.convex_polygon_shape_create(mesh)
             else:
                 self.shape_create(int(s["type"]), s["p"])
-        first = self.bodies_create(sc.bodies) if len(sc.bodies) else 0
+        bodies = sc.bodies
+        kin = bodies["mode"] == scenes.MODE_KINEMATIC
+        if kin.any():   # in a scene file a kinematic body's velocities are its motion script (oracle/ref_harness.cpp), not body state
+            bodies = bodies.copy()
+            bodies["linvel"][kin] = 0
+            bodies["angvel"][kin] = 0
+        first = self.bodies_create(bodies) if len(bodies) else 0
         if len(sc.joints):
             self.joints_create(sc.joints)
         return first

@@ -380,14 +380,20 @@ void BradotPhysicsServerCUDA::body_set_state(RID p_body, BodyState p_state, cons
 			body->xf = p_variant;
 			if (body->slot >= 0) {
 				_xf_to_floats(body->xf, f);
-				bpc_bodies_write(ctx, BPC_FIELD_TRANSFORM, body->slot, 1, f);
+				// a kinematic body is told where to be after the next step (new_transform, bradot_body_3d.cpp:355-364)
+				bpc_bodies_write(ctx, body->mode == BODY_MODE_KINEMATIC ? BPC_FIELD_KINEMATIC_TARGET : BPC_FIELD_TRANSFORM, body->slot, 1, f);
 			}
 		} break;
 		case BODY_STATE_LINEAR_VELOCITY:
 		case BODY_STATE_ANGULAR_VELOCITY: {
 			Vector3 v = p_variant;
 			(p_state == BODY_STATE_LINEAR_VELOCITY ? body->linvel : body->angvel) = v;
-			if (body->slot >= 0) {
+			if (body->slot >= 0 && body->mode == BODY_MODE_KINEMATIC) {
+				// constant_linear_velocity / constant_angular_velocity (bradot_body_3d.cpp:383-393)
+				f[0] = body->linvel.x; f[1] = body->linvel.y; f[2] = body->linvel.z;
+				f[3] = body->angvel.x; f[4] = body->angvel.y; f[5] = body->angvel.z;
+				bpc_bodies_write(ctx, BPC_FIELD_KINEMATIC_VELOCITY, body->slot, 1, f);
+			} else if (body->slot >= 0) {
 				f[0] = v.x;
 				f[1] = v.y;
 				f[2] = v.z;

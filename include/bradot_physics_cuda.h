@@ -59,7 +59,16 @@ enum {
     BPC_FIELD_MASS_PROPS = 4,       /* 16 floats: inv_mass, inv_inertia(3), com_local(3), principal axes rows(9) */
     BPC_FIELD_ITEM_BOX = 5,         /* 14 floats: aabb_cache pos(3) size(3), stored min(3) max(3), num_pairs, id */
     BPC_FIELD_APPLIED_FORCE = 6,    /* 6 floats: force, torque accumulated for the next step (body_apply_force/torque) */
-    BPC_FIELD_STILL_TIME = 7        /* 1 float */
+    BPC_FIELD_STILL_TIME = 7,       /* 1 float */
+    /* kinematic bodies (write only; ignored for bodies of other modes in the range):
+     * TARGET = the transform the body is to have after the next step: what body_set_state(BODY_STATE_TRANSFORM) means for a
+     * kinematic body (new_transform, modules/bradot_physics_3d/bradot_body_3d.cpp:354-364); it wakes the body.  The step
+     * derives the body's velocities from the move (bradot_body_3d.cpp:611-627).  BPC_FIELD_TRANSFORM on a kinematic body
+     * places it (current transform and target).
+     * VELOCITY = constant linear + angular velocity (6 floats) added to the derived ones: what BODY_STATE_LINEAR_VELOCITY /
+     * ANGULAR_VELOCITY mean for a kinematic body (constant_linear_velocity, bradot_body_3d.cpp:383-393). */
+    BPC_FIELD_KINEMATIC_TARGET = 8,
+    BPC_FIELD_KINEMATIC_VELOCITY = 9
 };
 
 typedef struct bpc_stats {

@@ -129,6 +129,11 @@ struct World {
 	std::vector<BradotBody3D *> body_ptr;
 	std::map<const BradotBody3D *, int> body_index;
 	std::vector<uint32_t> body_space;
+	// kinematic bodies: every step the harness sets transform(t) = (rotation about y by angvel.y t) * basis0, origin0 + linvel t
+	std::vector<int> kin_body;
+	std::vector<Transform3D> kin_xf0;
+	std::vector<Vector3> kin_lin;
+	std::vector<float> kin_wy;
 };
 
 #define PAIR_STRIDE 12
@@ -252,6 +257,30 @@ static void dump_step(Dump &d, World &w, int step) {
 		d.arr("stats", step, "i4", { 4 }, stats, sizeof(stats));
 	}
 	d.arr("solve_order", step, "i4", { (uint64_t)order.size() / 3, 3 }, order.data(), order.size() * 4);
+}
+
+// Move the kinematic bodies the way a game does: body_set_state(TRANSFORM) before the step (bradot_body_3d.cpp:354-364).
+// The targets are dumped ("kin_targets", step): (n_kinematic, 13) = body index, then the 12 floats of the transform.
+static void drive_kinematic(Dump &d, World &w, int step, float dt, bool dump) {
+	if (w.kin_body.empty()) {
+		return;
+	}
+	std::vector<float> out;
+	for (size_t i = 0; i < w.kin_body.size(); i++) {
+		real_t t = (real_t)step * dt;
+		Transform3D x;
+		x.basis = Basis(Vector3(0, 1, 0), w.kin_wy[i] * t) * w.kin_xf0[i].basis;
+		x.origin = w.kin_xf0[i].origin + w.kin_lin[i] * t;
+		w.ps->body_set_state(w.bodies[w.kin_body[i]], PhysicsServer3D::BODY_STATE_TRANSFORM, x);
+		out.push_back((float)w.kin_body[i]);
+		for (int r = 0; r < 3; r++) {
+			put3(out, x.basis.rows[r]);
+		}
+		put3(out, x.origin);
+	}
+	if (dump && d.f) {
+		d.arr("kin_targets", step, "f4", { (uint64_t)w.kin_body.size(), 13 }, out.data(), out.size() * 4);
+	}
 }
 
 // PhysicsDirectSpaceState3D::intersect_ray (bradot_space_3d.cpp:109-191) for every ray of the file, space 0
@@ -502,8 +531,10 @@ int main(int argc, char **argv) {
 		ps->body_set_collision_layer(body, b.layer);
 		ps->body_set_collision_mask(body, b.mask);
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_TRANSFORM, xf_from(b.xf));
-		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
-		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(b.angvel[0], b.angvel[1], b.angvel[2]));
+		if (b.mode != PhysicsServer3D::BODY_MODE_KINEMATIC) { // a kinematic body's scene velocities are its motion script (below)
+			ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
+			ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(b.angvel[0], b.angvel[1], b.angvel[2]));
+		}
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, (b.flags & 1) != 0);
 		if (b.flags & 2) {
 			ps->body_set_enable_continuous_collision_detection(body, true);
@@ -517,6 +548,12 @@ int main(int argc, char **argv) {
 		w.body_ptr.push_back(bp);
 		w.body_index[bp] = i;
 		w.body_space.push_back(b.space);
+		if (b.mode == PhysicsServer3D::BODY_MODE_KINEMATIC) {
+			w.kin_body.push_back(i);
+			w.kin_xf0.push_back(xf_from(b.xf));
+			w.kin_lin.push_back(Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
+			w.kin_wy.push_back(b.angvel[1]);
+		}
 	}
 	for (uint32_t i = 0; i < hd.n_joints; i++) {
 		const ScnJoint &j = sjoints[i];
@@ -556,6 +593,7 @@ int main(int argc, char **argv) {
 	double phase_us[5] = { 0, 0, 0, 0, 0 };
 	auto t0 = std::chrono::steady_clock::now();
 	for (int s = 1; s <= steps; s++) {
+		drive_kinematic(d, w, s, hd.dt, true);
 		ps->step(hd.dt);
 		for (RID sp : w.spaces) {
 			BradotSpace3D *space = ps->space_owner.get_or_null(sp);
