@@ -212,7 +212,8 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
         mass_properties(sh, d, props[i], inv_mass);
         memset(&mw[i], 0, sizeof(BodyMassW));
         mw[i].m = make_float4(inv_mass, d.friction, d.bounce, 0.f);
-        uint32_t flags = (d.flags & 1u ? BF_CAN_SLEEP : 0u) | (d.flags & 4u ? 0u : BF_ACTIVE);
+        uint32_t flags = (d.flags & 1u ? BF_CAN_SLEEP : 0u) | (d.flags & 4u ? 0u : BF_ACTIVE) | (d.flags & 2u ? BF_CCD : 0u);
+        if ((d.flags & 2u) && d.mode >= MODE_RIGID) ctx->h_ccd_ids.push_back(first + i);
         // a kinematic body is inactive until it is given somewhere to go (set_mode: bradot_body_3d.cpp:218-231), and its
         // velocities are whatever its moves imply
         if (d.mode == MODE_STATIC || d.mode == MODE_KINEMATIC) flags &= ~BF_ACTIVE;
@@ -246,6 +247,11 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
     BPC_CHECK(cudaMemsetAsync(ctx->items.p + first, 0, n * sizeof(ItemBox), st));
     BPC_CHECK(cudaMemsetAsync(ctx->npairs.p + first, 0, n * sizeof(uint32_t), st));
     ctx->n_bodies = (uint32_t)total;
+    if (!ctx->h_ccd_ids.empty()) {
+        ctx->ccd_ids.reserve(ctx->h_ccd_ids.size(), false, st);
+        if (!ctx->ccd_ids.p) return fail(ctx, "bpc_bodies_create: out of device memory");
+        BPC_CHECK(cudaMemcpyAsync(ctx->ccd_ids.p, ctx->h_ccd_ids.data(), ctx->h_ccd_ids.size() * 4, cudaMemcpyHostToDevice, st));
+    }
     if (!ctx->h_kin_ids.empty()) {
         ctx->kin.reserve(total, true, st);
         ctx->kin_ids.reserve(ctx->h_kin_ids.size(), false, st);

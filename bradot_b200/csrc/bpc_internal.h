@@ -174,6 +174,8 @@ struct bpc_context {
     DevBuf<KinState> kin;        // indexed by body; allocated when the first kinematic body is created
     DevBuf<uint32_t> kin_ids;    // the kinematic bodies
     std::vector<uint32_t> h_kin_ids;
+    DevBuf<uint32_t> ccd_ids;    // bodies with continuous collision detection
+    std::vector<uint32_t> h_ccd_ids;
     DevBuf<uint32_t> tree_items; // body ids that live in the LBVH (everything except unbounded statics)
     uint32_t n_tree = 0;
     DevBuf<uint32_t> island; // connected-component label per body

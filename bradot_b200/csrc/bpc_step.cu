@@ -39,11 +39,31 @@ __global__ void k_forced_lookup(uint32_t n, const uint64_t *__restrict__ fkeys, 
     order[i] = found ? lo : 0xffffffffu;
     if (found) mark[lo] = 1u;
 }
-// colliding pairs the forced order does not mention are NOT solved: report them
-__global__ void k_forced_missing(uint32_t n_pairs, const PairHdr *__restrict__ hdr, const uint32_t *__restrict__ mark, uint32_t *__restrict__ counters) {
+// Colliding pairs the forced order does not mention are NOT solved: report them.  A colliding pair none of whose contacts
+// has a positive depth is no constraint for the reference either (pre_solve returns false and the island drops it,
+// bradot_body_pair_3d.cpp:319-455, bradot_step_3d.cpp:121-132), so its absence from an imported order is expected.
+__global__ void k_forced_missing(uint32_t n_pairs, const PairHdr *__restrict__ hdr, const uint32_t *__restrict__ mark, const uint64_t *__restrict__ keys,
+                                 const BodyXf *__restrict__ xf, const ContactGeo *__restrict__ geo, const uint4 *__restrict__ meta,
+                                 uint32_t *__restrict__ counters) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n_pairs) return;
-    if ((__float_as_uint(hdr[k].sep.w) & 0x100u) && !mark[k]) atomicAdd(&counters[CNT_OVERFLOW], 1u);
+    uint32_t bits = __float_as_uint(hdr[k].sep.w);
+    if (!(bits & 0x100u) || mark[k]) return;
+    uint64_t key = keys[k];
+    // pairs of sleeping islands keep last step's flags and are nobody's constraints this step
+    uint4 ma = meta[(uint32_t)(key >> 32)], mb = meta[(uint32_t)key];
+    if (!((((ma.x & 0xffu) != MODE_STATIC ? ma.x : mb.x) >> 8) & BF_ISLAND_AWAKE)) return;
+    BodyXf xa = xf[(uint32_t)(key >> 32)], xb = xf[(uint32_t)key];
+    M3 bA(f4v(xa.r0), f4v(xa.r1), f4v(xa.r2)), bB(f4v(xb.r0), f4v(xb.r1), f4v(xb.r2));
+    V3 offset_B = f4v(xb.o) - f4v(xa.o);
+    bool any = false;
+    for (uint32_t c = 0; c < (bits & 0xffu); c++) {
+        ContactGeo g = geo[(size_t)k * 4 + c];
+        V3 gA = xform(bA, f4v(g.la));
+        V3 gB = xform(bB, f4v(g.lb)) + offset_B;
+        any = any || dot(gA - gB, f4v(g.n)) > 0.0f;
+    }
+    if (any) atomicAdd(&counters[CNT_OVERFLOW], 1u);
 }
 __global__ void k_count_collided(uint32_t n_pairs, const PairHdr *__restrict__ hdr, uint32_t *__restrict__ counters) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -60,7 +80,8 @@ static int forced_schedule(bpc_context *ctx) {
     if (!ctx->con_color.p || !ctx->forced_order.p) return fail(ctx, "out of device memory");
     if (np) BPC_CHECK(cudaMemsetAsync(ctx->con_color.p, 0, (size_t)np * 4, st));
     k_forced_lookup<<<nblk(n, 128), 128, 0, st>>>(n, ctx->forced_keys.p, np, ctx->pair_keys[ctx->cur].p, ctx->forced_order.p, ctx->con_color.p);
-    if (np) k_forced_missing<<<nblk(np, 128), 128, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->con_color.p, ctx->counters.p);
+    if (np) k_forced_missing<<<nblk(np, 128), 128, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->con_color.p, ctx->pair_keys[ctx->cur].p, ctx->xf.p,
+                                                          ctx->cgeo[ctx->cur].p, ctx->meta.p, ctx->counters.p);
     ctx->launches += 2;
     BPC_CHECK(cudaGetLastError());
     return 0;

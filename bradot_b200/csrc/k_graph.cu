@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(GR_THREADS) k_con_collect(uint32_t n_pairs, co
                                                             uint32_t *__restrict__ counters) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     bool take = false;
-    if (k < n_pairs && (__float_as_uint(hdr[k].sep.w) & 0x100u) != 0) {
+    if (k < n_pairs && (__float_as_uint(hdr[k].sep.w) & 0x900u) != 0) { // colliding, or to be tested for tunnelling (check_ccd)
         // pairs of sleeping islands keep last step's flags: they are not constraints of this step
         uint64_t key = keys[k];
         uint32_t a = (uint32_t)(key >> 32), b = (uint32_t)key;

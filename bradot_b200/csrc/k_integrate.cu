@@ -232,6 +232,40 @@ __device__ inline void basis_axis_angle(const M3 &m, V3 &axis, float &angle) {
     angle = cs < -1.f ? (float)3.14159265358979323846 : (cs > 1.f ? 0.f : (float)acos((double)cs));
 }
 
+// _update_shapes_with_motion (bradot_collision_object_3d.cpp:186-211): the shape box merged with itself moved by `motion`
+// (AABB::merge_with, core/math/aabb.cpp:49-74), no 5 % growth, handed to the broadphase like any move
+__device__ __forceinline__ void sweep_item(const BodyXf &x, const BodyXf &sx, const ShapeRec &sh, V3 motion, ItemBox &it, int np) {
+    X3 X = X3(load_basis(x), f4v(x.o)) * X3(load_basis(sx), f4v(sx.o));
+    Box3 la;
+    la.pos = f4v(sh.aabb_pos);
+    la.size = f4v(sh.aabb_size);
+    Box3 box = xform_aabb(X, la);
+    V3 beg_1 = box.pos, beg_2 = box.pos + motion, end_1 = box.size + beg_1, end_2 = box.size + beg_2;
+    V3 mn(beg_1.x < beg_2.x ? beg_1.x : beg_2.x, beg_1.y < beg_2.y ? beg_1.y : beg_2.y, beg_1.z < beg_2.z ? beg_1.z : beg_2.z);
+    V3 mx(end_1.x > end_2.x ? end_1.x : end_2.x, end_1.y > end_2.y ? end_1.y : end_2.y, end_1.z > end_2.z ? end_1.z : end_2.z);
+    box.pos = mn;
+    box.size = mx - mn;
+    it.cache_pos = v4(box.pos, 0.f);
+    it.cache_size = v4(box.size, 0.f);
+    store_item_box(box, it, np, false);
+}
+
+// integrate_forces, "if (continuous_cd)" (bradot_body_3d.cpp:656-659, 665-667): the box of a fast body covers this step's move
+__global__ void __launch_bounds__(IT_THREADS) k_ccd_forces(uint32_t n_ccd, const uint32_t *__restrict__ ids, float dt, const BodyXf *__restrict__ xf,
+                                                           const BodyVel *__restrict__ vel, const uint4 *__restrict__ meta,
+                                                           const BodyXf *__restrict__ shape_xf, const uint32_t *__restrict__ shape_id,
+                                                           const ShapeRec *__restrict__ shapes, ItemBox *__restrict__ items,
+                                                           const uint32_t *__restrict__ npairs) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_ccd) return;
+    uint32_t i = ids[t];
+    if (!((meta[i].x >> 8) & BF_ACTIVE)) return;
+    V3 motion = f4v(vel[i].lin) * dt;
+    ItemBox it = items[i];
+    sweep_item(xf[i], shape_xf[i], shapes[shape_id[i]], motion, it, (int)npairs[i]);
+    items[i] = it;
+}
+
 // integrate_forces of an active kinematic body (bradot_body_3d.cpp:611-627, 665-667): velocities from the move the host
 // asked for, and the broadphase box swept along the move (_update_shapes_with_motion, bradot_collision_object_3d.cpp:186-211)
 __global__ void __launch_bounds__(IT_THREADS) k_kinematic_forces(uint32_t n_kin, const uint32_t *__restrict__ ids, float dt, const BodyXf *__restrict__ xf,
@@ -255,23 +289,8 @@ __global__ void __launch_bounds__(IT_THREADS) k_kinematic_forces(uint32_t n_kin,
     V3 ang = f4v(k.cang) + axis * (angle / dt);
     vel[i].lin = v4(lin, 0.f);
     vel[i].ang = v4(ang, 0.f);
-    BodyXf sx = shape_xf[i];
-    X3 X = X3(load_basis(x), f4v(x.o)) * X3(load_basis(sx), f4v(sx.o));
-    const ShapeRec sh = shapes[shape_id[i]];
-    Box3 la;
-    la.pos = f4v(sh.aabb_pos);
-    la.size = f4v(sh.aabb_size);
-    Box3 box = xform_aabb(X, la);
-    // AABB::merge_with the same box moved by `motion` (core/math/aabb.cpp:49-74)
-    V3 beg_1 = box.pos, beg_2 = box.pos + motion, end_1 = box.size + beg_1, end_2 = box.size + beg_2;
-    V3 mn(beg_1.x < beg_2.x ? beg_1.x : beg_2.x, beg_1.y < beg_2.y ? beg_1.y : beg_2.y, beg_1.z < beg_2.z ? beg_1.z : beg_2.z);
-    V3 mx(end_1.x > end_2.x ? end_1.x : end_2.x, end_1.y > end_2.y ? end_1.y : end_2.y, end_1.z > end_2.z ? end_1.z : end_2.z);
-    box.pos = mn;
-    box.size = mx - mn;
     ItemBox it = items[i];
-    it.cache_pos = v4(box.pos, 0.f);
-    it.cache_size = v4(box.size, 0.f);
-    store_item_box(box, it, (int)npairs[i], false);
+    sweep_item(x, shape_xf[i], shapes[shape_id[i]], motion, it, (int)npairs[i]);
     items[i] = it;
 }
 
@@ -373,6 +392,12 @@ int bpc_launch_integrate_forces(bpc_context *ctx, float dt) {
     k_integrate_forces<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->vel.p, ctx->props.p, ctx->forces.p, ctx->massw.p,
                                                                             ctx->meta.p, ctx->d_spaces.p, ctx->counters.p);
     ctx->launches += 1;
+    uint32_t nc = (uint32_t)ctx->h_ccd_ids.size();
+    if (nc) {
+        k_ccd_forces<<<nblk(nc, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(nc, ctx->ccd_ids.p, dt, ctx->xf.p, ctx->vel.p, ctx->meta.p, ctx->shape_xf.p,
+                                                                           ctx->shape_id.p, ctx->shapes.p, ctx->items.p, ctx->npairs.p);
+        ctx->launches += 1;
+    }
     uint32_t nk = (uint32_t)ctx->h_kin_ids.size();
     if (nk) {
         k_kinematic_forces<<<nblk(nk, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(nk, ctx->kin_ids.p, dt, ctx->xf.p, ctx->kin.p, ctx->vel.p, ctx->meta.p,

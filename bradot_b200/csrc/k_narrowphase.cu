@@ -154,6 +154,9 @@ __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
                 }
             }
             if (!work && !cwork) {
+                // setup() still hands a non-colliding pair to the solver when a body with continuous collision detection
+                // takes part (check_ccd, bradot_body_pair_3d.cpp:302-311)
+                if (interacts && !excepted && ((((ma.x >> 8) & BF_CCD) && collide_A) || (((mb.x >> 8) & BF_CCD) && collide_B))) nb |= 0x800u;
                 h.sep.w = __uint_as_float(nb);
                 a.hdr[k] = h;
             }
@@ -230,6 +233,7 @@ __global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
         a.acc[(size_t)k * 4 + c] = ac;
     }
     uint32_t nb = (uint32_t)m.count | (collided ? 0x100u : 0u) | (collide_A ? 0x200u : 0u) | (collide_B ? 0x400u : 0u);
+    if (!collided && ((((ma.x >> 8) & BF_CCD) && collide_A) || (((mb.x >> 8) & BF_CCD) && collide_B))) nb |= 0x800u; // check_ccd
     h.sep = v4(sep_axis, __uint_as_float(nb));
     a.hdr[k] = h;
 }
@@ -316,6 +320,7 @@ __global__ void __launch_bounds__(CW_WARPS * 32) k_convex_warp(NpArgs a) {
         a.acc[(size_t)k * 4 + c] = ac;
     }
     uint32_t nb = (uint32_t)m.count | (collided ? 0x100u : 0u) | (collide_A ? 0x200u : 0u) | (collide_B ? 0x400u : 0u);
+    if (!collided && ((((ma.x >> 8) & BF_CCD) && collide_A) || (((mb.x >> 8) & BF_CCD) && collide_B))) nb |= 0x800u;
     h.sep = v4(sep_axis, __uint_as_float(nb));
     a.hdr[k] = h;
 }

@@ -8,7 +8,7 @@
 //   modules/bradot_physics_3d/bradot_step_3d.cpp:121-160        _pre_solve_island / _solve_island
 #include <cooperative_groups.h>
 
-#include "bpc_internal.h"
+#include "np_segment.cuh"
 namespace cg = cooperative_groups;
 
 #define SV_THREADS 128
@@ -39,6 +39,11 @@ struct SvArgs {
     size_t sc_stride;
     const JointRec *joints;
     const JointSetup *jsetup;
+    // continuous collision detection only
+    const BodyXf *shape_xf;
+    const float4 *shape_p;
+    const uint4 *medges;
+    MeshPools pools;
     float dt, inv_dt, max_bias_av;
     int iterations;
     uint32_t *counters;
@@ -84,14 +89,100 @@ __device__ __forceinline__ void apply_bias_impulse(BodyS &b, V3 j, V3 pos, float
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// BradotBodyPair3D::_test_ccd (bradot_body_pair_3d.cpp:172-254): a body that moves more than 0.3 of its extent along its
+// motion this step casts its leading support points forward; if one would pass through the other body's shape, the
+// linear velocity is cut so that the point lands just inside next step.  Kept out of line: bullets are rare.
+struct CcdShape {
+    Sh sh;      // for project_range / get_supports of the mover
+    QShape qs;  // for intersect_segment on the other body
+    X3 xf;      // basis * shape transform, origin relative to A's origin
+};
+
+__device__ __noinline__ void load_ccd_shape(const SvArgs &a, uint32_t body, uint32_t meta_x, const M3 &basis, V3 origin, CcdShape &out) {
+    out.xf = X3(basis, origin);
+    if (!((meta_x >> 8) & BF_SHAPE_IDENT)) {
+        BodyXf sx = a.shape_xf[body];
+        out.xf = out.xf * X3(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+    }
+    out.sh.type = meta_x >> 24;
+    out.sh.p = a.shape_p[body];
+    out.sh.m.nv = out.sh.m.nf = out.sh.m.ne = 0;
+    out.qs.type = out.sh.type;
+    out.qs.p = out.sh.p;
+    if (out.sh.type == SH_CONVEX) {
+        MeshRec m = a.pools.meshes[__float_as_uint(out.sh.p.x)];
+        out.qs.mesh = m;
+        out.sh.m.verts = a.pools.mverts + m.vert_ofs;
+        out.sh.m.planes = a.pools.mplanes + m.face_ofs;
+        out.sh.m.edges = a.medges + m.edge_ofs;
+        out.sh.m.faces = a.pools.mfaces + m.face_ofs;
+        out.sh.m.index = a.pools.mindex;
+        out.sh.m.nv = m.vert_cnt;
+        out.sh.m.nf = m.face_cnt;
+        out.sh.m.ne = m.edge_cnt;
+    }
+}
+
+__device__ __noinline__ void test_ccd(const SvArgs &a, uint32_t mover, const CcdShape &A, uint32_t other, const CcdShape &B) {
+    BodyVel vA = a.vel[mover];
+    V3 motion = f4v(vA.lin) * a.dt;
+    float mlen = length(motion);
+    if (mlen < CMP_EPSILON_F) return;
+    V3 mnormal = motion / mlen;
+    float mn = 0.f, mx = 0.f;
+    project_range(A.sh, mnormal, A.xf, mn, mx);
+    if (!((double)mlen > (double)(mx - mn) * 0.3)) return; // moving slowly enough that it cannot tunnel
+    X3 predicted_B = X3(B.xf.b, B.xf.o + f4v(a.vel[other].lin) * a.dt);
+    V3 sup[MAX_SUPPORTS];
+    int n = 0, type = FEATURE_POINT;
+    get_supports(A.sh, normalized(xform_inv(A.xf.b, mnormal)), sup, n, type);
+    int hit_idx = -1;
+    float hit_len = 3.402823466e+38f;
+    V3 hit_local;
+    X3 from_inv = affine_inverse(predicted_B);
+    for (int i = 0; i < n; i++) {
+        sup[i] = xform(A.xf, sup[i]);
+        V3 from = sup[i], to = from + motion;
+        V3 local_from = xform(from_inv, from - motion * 0.1f), local_to = xform(from_inv, to);
+        RayHit h;
+        if (q_shape_segment(a.pools, B.qs, local_from, local_to, h)) {
+            float len = length(h.point - local_from);
+            if (len < hit_len) {
+                hit_idx = i;
+                hit_len = len;
+                hit_local = h.point;
+            }
+        }
+    }
+    if (hit_idx < 0) return;
+    V3 hitpos = xform(predicted_B, hit_local);
+    float newlen = length(sup[hit_idx] - hitpos);
+    newlen = (float)((double)newlen + (double)(mx - mn) * 0.01);
+    vA.lin = v4((mnormal * newlen) / a.dt, 0.f);
+    a.vel[mover].lin = vA.lin;
+}
+
+__device__ __noinline__ void ccd_pair(const SvArgs &a, uint32_t ia, uint32_t ib, bool cA, bool cB) {
+    uint4 ma = a.meta[ia], mb = a.meta[ib];
+    BodyXf xa = a.xf[ia], xb = a.xf[ib];
+    CcdShape A, B;
+    load_ccd_shape(a, ia, ma.x, M3(f4v(xa.r0), f4v(xa.r1), f4v(xa.r2)), V3(), A);
+    load_ccd_shape(a, ib, mb.x, M3(f4v(xb.r0), f4v(xb.r1), f4v(xb.r2)), f4v(xb.o) - f4v(xa.o), B);
+    if (((ma.x >> 8) & BF_CCD) && cA) test_ccd(a, ia, A, ib, B);
+    if (((mb.x >> 8) & BF_CCD) && cB) test_ccd(a, ib, B, ia, A);
+}
+
 // pre_solve of one pair; writes SolveContact records at slot s and warm-starts the bodies
+template <bool CCD>
 __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
     uint64_t key = a.keys[k];
     uint32_t ia = (uint32_t)(key >> 32), ib = (uint32_t)key;
     uint32_t bits = __float_as_uint(a.hdr[k].sep.w);
     int count = bits & 0xffu;
     bool cA = bits & 0x200u, cB = bits & 0x400u;
-    if (!(bits & 0x100u)) { // not colliding this step (only reachable through a teacher-forced order)
+    if (!(bits & 0x100u)) { // not colliding this step: a pair kept for its tunnelling test, or one of a teacher-forced order
+        if (CCD && (bits & 0x800u)) ccd_pair(a, ia, ib, cA, cB);
         a.info[s] = make_uint4(ia, ib, 0u, k);
         return;
     }
@@ -444,6 +535,9 @@ __device__ inline void finish_pair(const SvArgs &a, uint32_t s) {
     }
 }
 
+// CCD = some body of the scene has continuous collision detection: only that variant carries the tunnelling test (its code
+// costs the common variant 13 % when it merely sits in the kernel)
+template <bool CCD>
 __global__ void __launch_bounds__(SV_THREADS) k_solve(SvArgs a) {
     cg::grid_group grid = cg::this_grid();
     uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
@@ -455,14 +549,14 @@ __global__ void __launch_bounds__(SV_THREADS) k_solve(SvArgs a) {
             if (tid == 0) {
                 for (uint32_t s = lo; s < hi; s++) {
                     uint32_t id = a.sched[s];
-                    if (id < a.n_pairs) pre_solve_pair(a, s, id);
+                    if (id < a.n_pairs) pre_solve_pair<CCD>(a, s, id);
                     else if (id != 0xffffffffu) pre_solve_joint(a, s, id - a.n_pairs);
                 }
             }
         } else {
             for (uint32_t s = lo + tid; s < hi; s += nth) {
                 uint32_t id = a.sched[s];
-                if (id < a.n_pairs) pre_solve_pair(a, s, id);
+                if (id < a.n_pairs) pre_solve_pair<CCD>(a, s, id);
                 else if (id != 0xffffffffu) pre_solve_joint(a, s, id - a.n_pairs);
             }
         }
@@ -558,18 +652,27 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     a.sc_stride = maxc;
     a.joints = ctx->d_joints.p;
     a.jsetup = ctx->jsetup.p;
+    a.shape_xf = ctx->shape_xf.p;
+    a.shape_p = ctx->shape_p.p;
+    a.medges = ctx->medges.p;
+    a.pools.meshes = ctx->meshes.p;
+    a.pools.mverts = ctx->mverts.p;
+    a.pools.mplanes = ctx->mplanes.p;
+    a.pools.mfaces = ctx->mfaces.p;
+    a.pools.mindex = ctx->mindex.p;
     a.dt = dt;
     a.inv_dt = (float)(1.0 / (double)dt);
     a.max_bias_av = (float)((3.14159265358979323846 / 8) / (double)dt);
     a.iterations = ctx->spaces.empty() ? 16 : ctx->spaces[0].iterations;
     a.counters = ctx->counters.p;
     int per_sm = 0;
-    BPC_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_solve, SV_THREADS, 0));
+    void *kernel = ctx->h_ccd_ids.empty() ? (void *)k_solve<false> : (void *)k_solve<true>;
+    BPC_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)kernel, SV_THREADS, 0));
     if (per_sm < 1) per_sm = 1;
     if (per_sm > 8) per_sm = 8;
     dim3 grid(ctx->sm_count * per_sm), block(SV_THREADS);
     void *args[] = { &a };
-    BPC_CHECK(cudaLaunchCooperativeKernel((void *)k_solve, grid, block, args, 0, st));
+    BPC_CHECK(cudaLaunchCooperativeKernel(kernel, grid, block, args, 0, st));
     ctx->launches += 1;
     return 0;
 }

@@ -1,0 +1,271 @@
+// Segment and point tests against one shape in its local frame, shared by the space queries (k_queries.cu) and the
+// continuous-collision test of the solver (k_solver.cu).
+//   modules/bradot_physics_3d/bradot_shape_3d.cpp:130-140 (world boundary) :279-285 (sphere) :421-429 (box)
+//     :555-619 (capsule) :979-1028 (convex polygon)          intersect_segment / intersect_point
+//   core/math/geometry_3d.h:86-276   segment_intersects_triangle / _sphere / _cylinder
+//   core/math/aabb.cpp:189-252       AABB::intersects_segment      core/math/plane.cpp:119-137  Plane::intersects_segment
+#pragma once
+#include "np_shapes.cuh"
+
+struct MeshPools {
+    const MeshRec *meshes;
+    const float4 *mverts;
+    const float4 *mplanes;
+    const uint2 *mfaces;
+    const uint32_t *mindex;
+};
+
+struct RayHit {
+    V3 point, normal;
+};
+
+// AABB::intersects_segment on a box given as (begin, end) per axis
+__device__ inline bool q_box_segment(V3 bmin, V3 bmax, V3 from, V3 to, V3 *r_point, V3 *r_normal) {
+    float mn = 0.f, mx = 1.f;
+    int axis = 0;
+    float sign = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        float seg_from = comp(from, i), seg_to = comp(to, i);
+        float box_begin = comp(bmin, i), box_end = comp(bmax, i);
+        float cmin, cmax, csign;
+        if (seg_from < seg_to) {
+            if (seg_from > box_end || seg_to < box_begin) return false;
+            float length = seg_to - seg_from;
+            cmin = (seg_from < box_begin) ? ((box_begin - seg_from) / length) : 0.f;
+            cmax = (seg_to > box_end) ? ((box_end - seg_from) / length) : 1.f;
+            csign = -1.0f;
+        } else {
+            if (seg_to > box_end || seg_from < box_begin) return false;
+            float length = seg_to - seg_from;
+            cmin = (seg_from > box_end) ? (box_end - seg_from) / length : 0.f;
+            cmax = (seg_to < box_begin) ? (box_begin - seg_from) / length : 1.f;
+            csign = 1.0f;
+        }
+        if (cmin > mn) {
+            mn = cmin;
+            axis = i;
+            sign = csign;
+        }
+        if (cmax < mx) mx = cmax;
+        if (mx < mn) return false;
+    }
+    if (r_normal) {
+        V3 n;
+        set_comp(n, axis, sign);
+        *r_normal = n;
+    }
+    if (r_point) *r_point = from + (to - from) * mn;
+    return true;
+}
+
+__device__ inline bool q_sphere_segment(V3 from, V3 to, V3 sphere_pos_in, float radius, RayHit &h) {
+    V3 sphere_pos = sphere_pos_in - from;
+    V3 rel = to - from;
+    float rel_l = length(rel);
+    if (rel_l < (float)BPC_CMP_EPSILON) return false;
+    V3 normal = rel / rel_l;
+    float sphere_d = dot(normal, sphere_pos);
+    V3 on_ray = normal * sphere_d;
+    float ray_distance = sqrtf(distance_squared(sphere_pos, on_ray));
+    if (ray_distance >= radius) return false;
+    float inters_d2 = radius * radius - ray_distance * ray_distance;
+    float inters_d = sphere_d;
+    if (inters_d2 >= (float)BPC_CMP_EPSILON) inters_d -= sqrtf(inters_d2);
+    if (inters_d < 0 || inters_d > rel_l) return false;
+    V3 result = from + normal * inters_d;
+    h.point = result;
+    h.normal = normalized(result - sphere_pos_in);
+    return true;
+}
+
+// Geometry3D::segment_intersects_cylinder with the axis along y (p_cylinder_axis = 1)
+__device__ inline bool q_cylinder_segment(V3 from, V3 to, float height, float radius, RayHit &h) {
+    V3 rel = to - from;
+    float rel_l = length(rel);
+    if (rel_l < (float)BPC_CMP_EPSILON) return false;
+    V3 cylinder_axis(0.f, 1.f, 0.f);
+    V3 normal = rel / rel_l;
+    V3 crs = cross(normal, cylinder_axis);
+    float crs_l = length(crs);
+    V3 axis_dir;
+    if (crs_l < (float)BPC_CMP_EPSILON) axis_dir = V3(0.f, 0.f, 1.f); // side axis (1 + 1) % 3
+    else axis_dir = crs / crs_l;
+    float dist = dot(axis_dir, from);
+    if (dist >= radius) return false;
+    float w2 = radius * radius - dist * dist;
+    if (w2 < (float)BPC_CMP_EPSILON) return false;
+    float size[2] = { sqrtf(w2), height * 0.5f };
+    V3 side_dir = normalized(cross(axis_dir, cylinder_axis));
+    float from2[2] = { dot(side_dir, from), from.y };
+    float to2[2] = { dot(side_dir, to), to.y };
+    float mn = 0.f, mx = 1.f;
+    int axis = -1;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        float seg_from = from2[i], seg_to = to2[i];
+        float box_begin = -size[i], box_end = size[i];
+        float cmin, cmax;
+        if (seg_from < seg_to) {
+            if (seg_from > box_end || seg_to < box_begin) return false;
+            float length = seg_to - seg_from;
+            cmin = (seg_from < box_begin) ? ((box_begin - seg_from) / length) : 0.f;
+            cmax = (seg_to > box_end) ? ((box_end - seg_from) / length) : 1.f;
+        } else {
+            if (seg_to > box_end || seg_from < box_begin) return false;
+            float length = seg_to - seg_from;
+            cmin = (seg_from > box_end) ? (box_end - seg_from) / length : 0.f;
+            cmax = (seg_to < box_begin) ? (box_begin - seg_from) / length : 1.f;
+        }
+        if (cmin > mn) {
+            mn = cmin;
+            axis = i;
+        }
+        if (cmax < mx) mx = cmax;
+        if (mx < mn) return false;
+    }
+    V3 result = from + (rel * mn);
+    V3 res_normal = result;
+    if (axis == 0) {
+        res_normal.y = 0.f;
+    } else {
+        res_normal.z = 0.f; // (axis + 1) % 3 and the one after it
+        res_normal.x = 0.f;
+    }
+    h.point = result;
+    h.normal = normalized(res_normal);
+    return true;
+}
+
+__device__ inline bool q_triangle_segment(V3 from, V3 to, V3 v0, V3 v1, V3 v2, V3 &res) {
+    V3 rel = to - from;
+    V3 e1 = v1 - v0, e2 = v2 - v0;
+    V3 hh = cross(rel, e2);
+    float a = dot(e1, hh);
+    if (is_zero_approx(a)) return false;
+    float f = 1.0f / a;
+    V3 s = from - v0;
+    float u = f * dot(s, hh);
+    if ((u < 0.0f) || (u > 1.0f)) return false;
+    V3 q = cross(s, e1);
+    float v = f * dot(rel, q);
+    if ((v < 0.0f) || (u + v > 1.0f)) return false;
+    float t = f * dot(e2, q);
+    if (t > (float)BPC_CMP_EPSILON && t <= 1.0f) {
+        res = from + rel * t;
+        return true;
+    }
+    return false;
+}
+
+struct QShape {
+    uint32_t type;
+    float4 p;
+    MeshRec mesh;
+};
+
+__device__ inline bool q_shape_point_inside(const MeshPools &a, const QShape &s, V3 p) {
+    switch (s.type) {
+        case SH_PLANE: return (dot(V3(s.p.x, s.p.y, s.p.z), p) - s.p.w) < 0;
+        case SH_SPHERE: return length(p) < s.p.x;
+        case SH_BOX: return fabsf(p.x) < s.p.x && fabsf(p.y) < s.p.y && fabsf(p.z) < s.p.z;
+        case SH_CAPSULE: {
+            float radius = s.p.x, height = s.p.y;
+            if (fabsf(p.y) < height * 0.5f - radius) return length(V3(p.x, 0.f, p.z)) < radius;
+            V3 q = p;
+            q.y = fabsf(q.y) - height * 0.5f + radius;
+            return length(q) < radius;
+        }
+        default: {
+            for (uint32_t i = 0; i < s.mesh.face_cnt; i++) {
+                float4 pl = a.mplanes[s.mesh.face_ofs + i];
+                if (dot(V3(pl.x, pl.y, pl.z), p) - pl.w >= 0) return false;
+            }
+            return true;
+        }
+    }
+}
+
+__device__ inline bool q_shape_segment(const MeshPools &a, const QShape &s, V3 from, V3 to, RayHit &h) {
+    switch (s.type) {
+        case SH_PLANE: { // Plane::intersects_segment
+            V3 n(s.p.x, s.p.y, s.p.z);
+            V3 segment = from - to;
+            float den = dot(n, segment);
+            if (is_zero_approx(den)) return false;
+            float dist = (dot(n, from) - s.p.w) / den;
+            if (dist < -(float)BPC_CMP_EPSILON || dist > (1.0f + (float)BPC_CMP_EPSILON)) return false;
+            dist = -dist;
+            h.point = from + segment * dist;
+            h.normal = n;
+            return true;
+        }
+        case SH_SPHERE: return q_sphere_segment(from, to, V3(), s.p.x, h);
+        case SH_BOX: {
+            V3 he(s.p.x, s.p.y, s.p.z);
+            V3 pos = -he, size = he * 2.0f;
+            return q_box_segment(pos, pos + size, from, to, &h.point, &h.normal);
+        }
+        case SH_CAPSULE: {
+            float radius = s.p.x, height = s.p.y;
+            V3 norm = normalized(to - from);
+            float min_d = 1e20f;
+            bool collision = false;
+            RayHit aux;
+            if (q_cylinder_segment(from, to, height - radius * 2.0f, radius, aux)) {
+                float d = dot(norm, aux.point);
+                if (d < min_d) {
+                    min_d = d;
+                    h = aux;
+                    collision = true;
+                }
+            }
+            if (q_sphere_segment(from, to, V3(0.f, height * 0.5f - radius, 0.f), radius, aux)) {
+                float d = dot(norm, aux.point);
+                if (d < min_d) {
+                    min_d = d;
+                    h = aux;
+                    collision = true;
+                }
+            }
+            if (q_sphere_segment(from, to, V3(0.f, height * -0.5f + radius, 0.f), radius, aux)) {
+                float d = dot(norm, aux.point);
+                if (d < min_d) {
+                    min_d = d;
+                    h = aux;
+                    collision = true;
+                }
+            }
+            return collision;
+        }
+        default: { // convex polygon: fan of every face that looks towards the ray
+            V3 n = to - from;
+            float mn = 1e20f;
+            bool col = false;
+            for (uint32_t i = 0; i < s.mesh.face_cnt; i++) {
+                float4 pl = a.mplanes[s.mesh.face_ofs + i];
+                V3 fn(pl.x, pl.y, pl.z);
+                if (dot(fn, n) > 0) continue;
+                uint2 f = a.mfaces[s.mesh.face_ofs + i];
+                V3 v0 = f4v(a.mverts[s.mesh.vert_ofs + a.mindex[f.x]]);
+                for (uint32_t j = 1; j + 1 < f.y; j++) {
+                    V3 v1 = f4v(a.mverts[s.mesh.vert_ofs + a.mindex[f.x + j]]);
+                    V3 v2 = f4v(a.mverts[s.mesh.vert_ofs + a.mindex[f.x + j + 1]]);
+                    V3 result;
+                    if (q_triangle_segment(from, to, v0, v1, v2, result)) {
+                        float d = dot(n, result);
+                        if (d < mn) {
+                            mn = d;
+                            h.point = result;
+                            h.normal = fn;
+                            col = true;
+                        }
+                        break;
+                    }
+                }
+            }
+            return col;
+        }
+    }
+}
+

@@ -399,3 +399,36 @@ def kinematic_platform():
     shape = np.where(np.arange(9) % 2 == 0, box, ball).astype(np.uint32)
     sc.add_bodies(9, shape=shape, xf=xf, mass=1.0)
     return sc
+
+
+def bullets(n=12):
+    """Continuous collision detection: small fast spheres and boxes (60 m/s = 1 m per step, five times their size) fired at a
+    thin static wall (every second one has the CCD flag, the others tunnel) and, one CCD bullet each, at three thin
+    free-floating plates (a plate has no other contact, so the order of its pre-solve among others cannot matter)."""
+    sc = Scene(name="bullets")
+    sc.add_static_plane((0, 1, 0), -5.0)
+    wall = sc.add_shape(SHAPE_BOX, (3.0, 3.0, 0.02, 0))
+    plate = sc.add_shape(SHAPE_BOX, (1.0, 1.0, 0.03, 0))
+    ball = sc.add_shape(SHAPE_SPHERE, (0.1, 0, 0, 0))
+    cube = sc.add_shape(SHAPE_BOX, (0.08, 0.08, 0.08, 0))
+    sc.add_bodies(1, mode=MODE_STATIC, shape=wall)
+    px = np.array([6.0, 9.0, 12.0])
+    xp = np.tile(IDENT12, (3, 1))
+    xp[:, 9] = px
+    sc.add_bodies(3, shape=plate, xf=xp, mass=5.0, gravity_scale=0.0)
+    rng = np.random.default_rng(4)
+    xf = np.tile(IDENT12, (n, 1))
+    xf[:, 9] = rng.uniform(-2.0, 2.0, n)
+    xf[:, 10] = rng.uniform(-1.5, 1.5, n)
+    xf[:, 11] = -rng.uniform(2.3, 7.7, n)
+    shape = np.where(np.arange(n) % 3 == 0, cube, ball).astype(np.uint32)
+    flags = np.where(np.arange(n) % 2 == 0, 3, 1).astype(np.uint32)   # bit1 = continuous cd
+    lin = np.zeros((n, 3), np.float32)
+    lin[:, 2] = 60.0
+    sc.add_bodies(n, shape=shape, xf=xf, flags=flags, linvel=lin, mass=0.2, gravity_scale=0.0)
+    xb = np.tile(IDENT12, (3, 1))
+    xb[:, 9] = px + np.array([0.3, -0.2, 0.45])
+    xb[:, 10] = np.array([0.2, -0.4, 0.1])
+    xb[:, 11] = -np.array([3.3, 5.6, 4.45])
+    sc.add_bodies(3, shape=np.array([ball, cube, ball], np.uint32), xf=xb, flags=3, linvel=(0.0, 0.0, 60.0), mass=0.2, gravity_scale=0.0)
+    return sc

@@ -28,7 +28,7 @@ enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1 };
  * body_set_mode / body_add_shape / body_set_param / body_set_state / body_set_space
  * (P3D/bradot_physics_server_3d.cpp:438-760). */
 typedef struct bpc_body_desc {
-    uint32_t space, mode, shape, flags; /* flags: bit0 can_sleep, bit1 continuous cd (ignored), bit2 start asleep */
+    uint32_t space, mode, shape, flags; /* flags: bit0 can_sleep, bit1 continuous collision detection, bit2 start asleep */
     float xf[12];                       /* basis rows (9) then origin (3) */
     float shape_xf[12];                 /* local transform of the single shape */
     float linvel[3], angvel[3];

@@ -191,7 +191,7 @@ static void dump_step(Dump &d, World &w, int step) {
 			pi.push_back(w.body_index[p->A]);
 			pi.push_back(w.body_index[p->B]);
 			pi.push_back(p->contact_count);
-			pi.push_back((p->collided ? 1 : 0) | (p->collide_A ? 2 : 0) | (p->collide_B ? 4 : 0));
+			pi.push_back((p->collided ? 1 : 0) | (p->collide_A ? 2 : 0) | (p->collide_B ? 4 : 0) | (p->check_ccd ? 8 : 0));
 			put3(pf, p->sep_axis);
 			put3(pf, p->offset_B);
 			for (int c = 0; c < 4; c++) {
