@@ -317,12 +317,18 @@ __global__ void k_pack_vel(uint32_t n, const BodyVel *__restrict__ vel, int angu
     float4 v = angular ? vel[i].ang : vel[i].lin;
     out[(size_t)i * 3] = v.x; out[(size_t)i * 3 + 1] = v.y; out[(size_t)i * 3 + 2] = v.z;
 }
-__global__ void k_unpack_forces(uint32_t n, const float *__restrict__ in, BodyForces *__restrict__ forces) {
+// body_apply_*force / body_apply_torque wake the body (bradot_physics_server_3d.cpp:859-897 -> wakeup()); a bulk write
+// carries a row for every body, so here a row wakes its body when it holds a non-zero force or torque
+__global__ void k_unpack_forces(uint32_t n, const float *__restrict__ in, BodyForces *__restrict__ forces, uint4 *__restrict__ meta) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float *o = in + (size_t)i * 6;
     forces[i].force = make_float4(o[0], o[1], o[2], 0.f);
     forces[i].torque = make_float4(o[3], o[4], o[5], 0.f);
+    if (o[0] != 0.f || o[1] != 0.f || o[2] != 0.f || o[3] != 0.f || o[4] != 0.f || o[5] != 0.f) {
+        uint32_t m = meta[i].x;
+        if ((m & 0xffu) >= MODE_RIGID && !((m >> 8) & BF_ACTIVE)) meta[i].x = m | (BF_ACTIVE << 8);
+    }
 }
 static int staging_for(bpc_context *ctx, size_t floats) {
     ctx->staging.reserve(floats, false, ctx->stream);
@@ -525,7 +531,7 @@ extern "C" int bpc_bodies_write(bpc_context *ctx, int field, int first, int n, c
         case BPC_FIELD_APPLIED_FORCE: {
             if (staging_for(ctx, (size_t)n * 6)) return -1;
             BPC_CHECK(cudaMemcpyAsync(ctx->staging.p, in, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-            k_unpack_forces<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->staging.p, ctx->forces.p + first);
+            k_unpack_forces<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->staging.p, ctx->forces.p + first, ctx->meta.p + first);
             BPC_CHECK(cudaStreamSynchronize(ctx->stream)); // the caller may reuse its buffer right away
         } break;
     }

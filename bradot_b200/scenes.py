@@ -432,3 +432,27 @@ def bullets(n=12):
     xb[:, 11] = -np.array([3.3, 5.6, 4.45])
     sc.add_bodies(3, shape=np.array([ball, cube, ball], np.uint32), xf=xb, flags=3, linvel=(0.0, 0.0, 60.0), mass=0.2, gravity_scale=0.0)
     return sc
+
+
+PUSH_FLAG = 8   # scene flag bit3: the harness applies a force and a torque to the body before every step
+
+
+def pushed_force(i):
+    """The push oracle/ref_harness.cpp (push_bodies) gives body i: (force xyz, torque xyz)."""
+    return np.array([0.5 * ((i % 3) - 1), 2.0, 0.3, 0.1, 0.0, 0.05 * (i % 2)], np.float32)
+
+
+def pushed(n=24):
+    """body_apply_central_force / body_apply_torque every step on boxes and spheres resting on or floating above a plane."""
+    sc = Scene(name="pushed")
+    sc.add_static_plane((0, 1, 0), 0.0)
+    box = sc.add_shape(SHAPE_BOX, (0.3, 0.2, 0.25, 0))
+    ball = sc.add_shape(SHAPE_SPHERE, (0.25, 0, 0, 0))
+    xf = np.tile(IDENT12, (n, 1))
+    xf[:, 9] = (np.arange(n) % 6 - 2.5) * 1.5
+    xf[:, 11] = (np.arange(n) // 6 - 1.5) * 1.5
+    xf[:, 10] = np.where(np.arange(n) % 4 == 0, 2.0, 0.26)
+    shape = np.where(np.arange(n) % 2 == 0, box, ball).astype(np.uint32)
+    flags = np.where(np.arange(n) % 5 == 4, 1, 1 | PUSH_FLAG).astype(np.uint32)
+    sc.add_bodies(n, shape=shape, xf=xf, flags=flags, mass=1.5)
+    return sc

@@ -58,7 +58,7 @@ enum {
     BPC_FIELD_ACTIVE = 3,           /* 1 float (0/1)                           (BODY_STATE_SLEEPING, inverted) */
     BPC_FIELD_MASS_PROPS = 4,       /* 16 floats: inv_mass, inv_inertia(3), com_local(3), principal axes rows(9) */
     BPC_FIELD_ITEM_BOX = 5,         /* 14 floats: aabb_cache pos(3) size(3), stored min(3) max(3), num_pairs, id */
-    BPC_FIELD_APPLIED_FORCE = 6,    /* 6 floats: force, torque accumulated for the next step (body_apply_force/torque) */
+    BPC_FIELD_APPLIED_FORCE = 6,    /* 6 floats: force, torque accumulated for the next step (body_apply_force/torque); a non-zero row wakes its body */
     BPC_FIELD_STILL_TIME = 7,       /* 1 float */
     /* kinematic bodies (write only; ignored for bodies of other modes in the range):
      * TARGET = the transform the body is to have after the next step: what body_set_state(BODY_STATE_TRANSFORM) means for a

@@ -70,7 +70,7 @@ struct ScnShape {
 	uint32_t pad;
 };
 struct ScnBody {
-	uint32_t space, mode, shape, flags; // flags bit0 can_sleep, bit1 ccd, bit2 start asleep
+	uint32_t space, mode, shape, flags; // flags bit0 can_sleep, bit1 ccd, bit2 start asleep, bit3 pushed every step (see push_bodies)
 	float xf[12]; // basis rows (9) + origin
 	float shape_xf[12];
 	float linvel[3], angvel[3];
@@ -134,6 +134,7 @@ struct World {
 	std::vector<Transform3D> kin_xf0;
 	std::vector<Vector3> kin_lin;
 	std::vector<float> kin_wy;
+	std::vector<uint32_t> body_flags;
 };
 
 #define PAIR_STRIDE 12
@@ -257,6 +258,19 @@ static void dump_step(Dump &d, World &w, int step) {
 		d.arr("stats", step, "i4", { 4 }, stats, sizeof(stats));
 	}
 	d.arr("solve_order", step, "i4", { (uint64_t)order.size() / 3, 3 }, order.data(), order.size() * 4);
+}
+
+// Bodies with flag bit3 are pushed the way a game pushes a vehicle: body_apply_central_force + body_apply_torque before
+// every step (accumulators cleared by the step, bradot_body_3d.cpp:661-662), with values that depend on the body index
+// only: F = (0.5 (i % 3 - 1), 2, 0.3) N, T = (0.1, 0, 0.05 (i % 2)) N m.
+static void push_bodies(World &w, const std::vector<uint32_t> &flags) {
+	for (size_t i = 0; i < w.bodies.size(); i++) {
+		if (!(flags[i] & 8)) {
+			continue;
+		}
+		w.ps->body_apply_central_force(w.bodies[i], Vector3(0.5f * (float)((int)(i % 3) - 1), 2.0f, 0.3f));
+		w.ps->body_apply_torque(w.bodies[i], Vector3(0.1f, 0.0f, 0.05f * (float)(i % 2)));
+	}
 }
 
 // Move the kinematic bodies the way a game does: body_set_state(TRANSFORM) before the step (bradot_body_3d.cpp:354-364).
@@ -548,6 +562,7 @@ int main(int argc, char **argv) {
 		w.body_ptr.push_back(bp);
 		w.body_index[bp] = i;
 		w.body_space.push_back(b.space);
+		w.body_flags.push_back(b.flags);
 		if (b.mode == PhysicsServer3D::BODY_MODE_KINEMATIC) {
 			w.kin_body.push_back(i);
 			w.kin_xf0.push_back(xf_from(b.xf));
@@ -594,6 +609,7 @@ int main(int argc, char **argv) {
 	auto t0 = std::chrono::steady_clock::now();
 	for (int s = 1; s <= steps; s++) {
 		drive_kinematic(d, w, s, hd.dt, true);
+		push_bodies(w, w.body_flags);
 		ps->step(hd.dt);
 		for (RID sp : w.spaces) {
 			BradotSpace3D *space = ps->space_owner.get_or_null(sp);

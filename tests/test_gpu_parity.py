@@ -269,6 +269,41 @@ def test_continuous_collision_detection_matches_the_reference():
     assert np.max(np.abs(z - ref_z)) < 0.05, np.abs(z - ref_z).max()
 
 
+def test_applied_forces_and_torques_match_the_reference():
+    """a2, the force accumulators: body_apply_central_force / body_apply_torque before every step (BPC_FIELD_APPLIED_FORCE
+    through the C ABI), consumed and cleared by the step."""
+    _need_oracle()
+    sc = scenes.pushed()
+    steps = 90
+    _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1)
+    push = np.zeros((len(sc.bodies), 6), np.float32)
+    for i in np.nonzero(sc.bodies["flags"] & scenes.PUSH_FLAG)[0]:
+        push[i] = scenes.pushed_force(int(i))
+    ps = parity.new_server(sc, dump)
+    worst = 0.0
+    for k in range(1, steps - 1):
+        parity.load_state(ps, dump, k)
+        ps.bodies_write(server.FIELD_APPLIED_FORCE, push)
+        ps.set_solve_order(parity.solve_order(dump, k + 1))
+        ps.step(sc.dt)
+        ref = dump[("bodies", k + 1)]
+        worst = max(worst, parity.rel_err(ps.bodies_read(server.FIELD_TRANSFORM), ref[:, 0:12], 1.0),
+                    parity.rel_err(ps.bodies_read(server.FIELD_LINEAR_VELOCITY), ref[:, 12:15], 1.0),
+                    parity.rel_err(ps.bodies_read(server.FIELD_ANGULAR_VELOCITY), ref[:, 15:18], 1.0))
+    assert worst < STATE_TOL, worst
+    # the accumulators are cleared by the step: one more step without a push is a step without force
+    parity.load_state(ps, dump, 10)
+    ps.bodies_write(server.FIELD_APPLIED_FORCE, push)
+    ps.step(sc.dt)
+    v1 = ps.bodies_read(server.FIELD_LINEAR_VELOCITY).copy()
+    ps.step(sc.dt)
+    v2 = ps.bodies_read(server.FIELD_LINEAR_VELOCITY)
+    floating = np.nonzero((sc.bodies["flags"] & scenes.PUSH_FLAG) != 0)[0]
+    floating = [i for i in floating if dump[("bodies", 10)][i, 10] > 1.0]      # in the air: only gravity acts in the second step
+    assert len(floating) > 0 and np.all(np.abs((v2[floating, 0] - v1[floating, 0])) < 1e-3 * (1 + np.abs(v1[floating, 0])))
+    ps.finish()
+
+
 def test_teacher_forced_joint_chains():     # pin + hinge chains of convex hulls (C4 layout), linked bodies excepted from colliding
     _need_oracle()
     sc = scenes.convex_chains(n_chains=9, chain_len=5, n_hulls=4)
