@@ -37,7 +37,7 @@ EXPORTS = [
     "bpc_shape_create", "bpc_shape_create_convex", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
     "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
-    "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points",
+    "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
 
@@ -79,6 +79,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_step.argtypes = [vp, cf]
     lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
     lib.bpc_space_intersect_points.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp, vp]
+    lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, ci, vp, vp]
     lib.bpc_synchronize.argtypes = [vp]
     lib.bpc_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
     lib.bpc_pair_count.argtypes = [vp]
@@ -248,6 +249,17 @@ class PhysicsServerCUDA:
         bodies = np.full((len(p), max_results), -1, np.int32)
         self._check(self.lib.bpc_space_intersect_points(self.ctx, int(space), len(p), _ptr(p), ctypes.c_uint(collision_mask), int(max_results),
                                                         _ptr(counts), _ptr(bodies)))
+        return counts, bodies
+
+    def intersect_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=32):
+        """Batched PhysicsDirectSpaceState3D.intersect_shape: shape handles (n) placed at xforms (n, 12)."""
+        sh = np.ascontiguousarray(shapes, np.int32).reshape(-1)
+        xf = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
+        assert len(sh) == len(xf)
+        counts = np.zeros(len(sh), np.int32)
+        bodies = np.full((len(sh), max_results), -1, np.int32)
+        self._check(self.lib.bpc_space_intersect_shapes(self.ctx, int(space), len(sh), _ptr(sh), _ptr(xf), ctypes.c_uint(collision_mask),
+                                                        int(max_results), _ptr(counts), _ptr(bodies)))
         return counts, bodies
 
     def set_solve_order(self, order):

@@ -215,6 +215,41 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_
 	return cc;
 }
 
+int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) {
+	ERR_FAIL_NULL_V(server, 0);
+	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.margin != 0.0, 0,
+			"BradotPhysicsCUDA: intersect_shape with exclude lists, areas or a margin is not supported yet.");
+	if (p_result_max <= 0 || !p_parameters.collide_with_bodies) {
+		return 0;
+	}
+	BradotPhysicsServerCUDA::Shape *shape = server->shape_owner.get_or_null(p_parameters.shape_rid);
+	ERR_FAIL_NULL_V(shape, 0);
+	int32_t handle = server->_shape_handle(shape);
+	ERR_FAIL_COND_V(handle < 0, 0);
+	server->_flush_pending();
+	int max_r = p_result_max > 2048 ? 2048 : p_result_max;
+	float f[12];
+	_xf_to_floats(p_parameters.transform, f);
+	int32_t count = 0;
+	LocalVector<int32_t> slots;
+	slots.resize(max_r);
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	int cc = 0;
+	for (int i = 0; i < count; i++) {
+		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size()) {
+			continue;
+		}
+		if (r_results) {
+			r_results[cc].rid = server->body_of_slot[slots[i]]->self;
+			r_results[cc].collider_id = ObjectID();
+			r_results[cc].collider = nullptr;
+			r_results[cc].shape = 0;
+		}
+		cc++;
+	}
+	return cc;
+}
+
 bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_parameters, RayResult &r_result) {
 	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.pick_ray, false,
 			"BradotPhysicsCUDA: intersect_ray with exclude lists, areas or pick_ray is not supported yet.");

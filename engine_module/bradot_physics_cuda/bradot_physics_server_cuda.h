@@ -33,7 +33,7 @@ public:
 	virtual bool intersect_ray(const RayParameters &p_parameters, RayResult &r_result) override;
 	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit);
 	virtual int intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
-	virtual int intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) override { BPC_UNSUPPORTED("intersect_shape"); return 0; }
+	virtual int intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
 	virtual bool cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info = nullptr) override { BPC_UNSUPPORTED("cast_motion"); return false; }
 	virtual bool collide_shape(const ShapeParameters &p_parameters, Vector3 *r_results, int p_result_max, int &r_result_count) override { BPC_UNSUPPORTED("collide_shape"); r_result_count = 0; return false; }
 	virtual bool rest_info(const ShapeParameters &p_parameters, ShapeRestInfo *r_info) override { BPC_UNSUPPORTED("rest_info"); return false; }

@@ -164,6 +164,13 @@ int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *fr
 int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int max_results,
                                int32_t *out_counts, int32_t *out_bodies);
 
+/* PhysicsDirectSpaceState3D::intersect_shape (servers/physics_server_3d.h:183-205; implementation
+ * modules/bradot_physics_3d/bradot_space_3d.cpp:208-262), batched: query i is shape handle shapes[i] (from bpc_shape_create*)
+ * placed at xforms[i] (12 floats, basis rows + origin); the answer lists the bodies whose shape it overlaps (margin 0).
+ * Output layout as bpc_space_intersect_points. */
+int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
+                               int max_results, int32_t *out_counts, int32_t *out_bodies);
+
 /* ---- utilities exposed for tests and tools */
 /* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */
 int bpc_sort_u64(bpc_context *ctx, const uint64_t *keys_in, uint64_t *keys_out, int n);

@@ -345,6 +345,47 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 		}
 	}
 	d.arr("points", step, "i4", { (uint64_t)n, 9 }, pts.data(), pts.size() * 4);
+	// intersect_shape (bradot_space_3d.cpp:208-262): query i uses shape i % 3 of {sphere 0.35, box (0.3, 0.2, 0.25), capsule r 0.2
+	// h 0.9} at the ray's origin, turned about the ray's direction by 0.37 i.  The transforms are dumped so that the other
+	// side asks with the same floats.
+	static RID qshape[3];
+	if (!qshape[0].is_valid()) {
+		qshape[0] = w.ps->sphere_shape_create();
+		w.ps->shape_set_data(qshape[0], 0.35f);
+		qshape[1] = w.ps->box_shape_create();
+		w.ps->shape_set_data(qshape[1], Vector3(0.3f, 0.2f, 0.25f));
+		qshape[2] = w.ps->capsule_shape_create();
+		Dictionary cd;
+		cd["radius"] = 0.2f;
+		cd["height"] = 0.9f;
+		w.ps->shape_set_data(qshape[2], cd);
+	}
+	std::vector<int32_t> sq(n * 9, -1);
+	std::vector<float> sxf;
+	for (size_t i = 0; i < n; i++) {
+		Vector3 from(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]), to(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+		Vector3 axis = (to - from).normalized();
+		if (axis == Vector3()) {
+			axis = Vector3(0, 1, 0);
+		}
+		PhysicsDirectSpaceState3D::ShapeParameters sp;
+		sp.shape_rid = qshape[i % 3];
+		sp.transform = Transform3D(Basis(axis, 0.37f * (float)i), from);
+		sp.collision_mask = 0xffffffffu;
+		PhysicsDirectSpaceState3D::ShapeResult sr[8];
+		int cc = ds ? ds->intersect_shape(sp, sr, 8) : 0;
+		sq[i * 9] = cc;
+		for (int k = 0; k < cc; k++) {
+			auto it = rid_index.find(sr[k].rid);
+			sq[i * 9 + 1 + k] = it == rid_index.end() ? -1 : it->second;
+		}
+		for (int r = 0; r < 3; r++) {
+			put3(sxf, sp.transform.basis.rows[r]);
+		}
+		put3(sxf, sp.transform.origin);
+	}
+	d.arr("shape_queries", step, "i4", { (uint64_t)n, 9 }, sq.data(), sq.size() * 4);
+	d.arr("shape_query_xf", step, "f4", { (uint64_t)n, 12 }, sxf.data(), sxf.size() * 4);
 }
 
 static void dump_meshes(Dump &d, World &w) {

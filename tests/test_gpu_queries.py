@@ -104,3 +104,31 @@ def test_intersect_points_against_the_reference():
         assert differ <= n // 1000, (k, differ)      # a point within rounding of a surface may flip
     assert inside > 1000
     ps.finish()
+
+
+def test_intersect_shapes_against_the_reference():
+    """intersect_shape: spheres, boxes and capsules placed at 3 000 poses (the harness's, dumped as "shape_query_xf") in a
+    mixed pile and in a hull pile; the set of overlapped bodies equals the reference's."""
+    parity_needed()
+    for sc, seed in ((scenes.mixed_pile(5, half=3.5), 12), (scenes.convex_pile(4), 13)):
+        rays = _rays(3000, seed, 3.4, 4.0)
+        _, dump = parity.run_oracle(sc, 60, dump_from=0, dump_every=1, rays=rays)
+        ps = parity.new_server(sc, dump)
+        handles = np.array([ps.sphere_shape_create(0.35), ps.box_shape_create((0.3, 0.2, 0.25)), ps.capsule_shape_create(0.2, 0.9)], np.int32)
+        shape_of = handles[np.arange(len(rays)) % 3]
+        overlaps = 0
+        for k in (1, 30, 59):
+            parity.load_state(ps, dump, k)
+            counts, bodies = ps.intersect_shapes(shape_of, dump[("shape_query_xf", k)], max_results=8)
+            ref = dump[("shape_queries", k)]
+            differ = 0
+            for i in range(len(rays)):
+                if ref[i, 0] >= 8 or counts[i] >= 8:
+                    continue                    # the cut at max_results follows each side's own tree order
+                a = set(bodies[i, :counts[i]].tolist())
+                b = set(ref[i, 1:1 + ref[i, 0]].tolist())
+                differ += a != b
+                overlaps += len(b)
+            assert differ <= len(rays) // 1000, (k, differ)     # a shape touching within rounding may flip
+        assert overlaps > 1500
+        ps.finish()
