@@ -66,10 +66,16 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_union_runs(uint32_t n, const 
     if (a >= n) return;
     uint32_t k = a_begin[a], ke = a_end[a];
     if (k >= ke || (meta[a].x & 0xffu) == MODE_STATIC) return;
-    for (; k < ke; k++) { // (keeping a's root across the run was measured slower: stale roots cost more CAS retries than the finds saved)
+    // (keeping a's ROOT across the run was measured slower: stale roots cost more CAS retries than the finds saved.)
+    // Early-out: a label is always an ancestor, so equal labels mean "already in one tree" -- one load instead of two finds
+    // for the many pairs inside an island that is already connected.
+    uint32_t la = ((volatile uint32_t *)label)[a];
+    for (; k < ke; k++) {
         uint32_t b = (uint32_t)keys[k];
         if ((meta[b].x & 0xffu) == MODE_STATIC) continue;
+        if (((volatile uint32_t *)label)[b] == la) continue;
         cc_union(label, a, b);
+        la = ((volatile uint32_t *)label)[a];
     }
 }
 
