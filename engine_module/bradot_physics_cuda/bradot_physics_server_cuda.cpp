@@ -544,6 +544,7 @@ void BradotPhysicsServerCUDA::free(RID p_rid) {
 		Body *b = body_owner.get_or_null(p_rid);
 		ERR_FAIL_COND_MSG(b->slot >= 0, "BradotPhysicsCUDA: removing an uploaded body is not supported yet.");
 		pending_bodies.erase(b);
+		pushed_bodies.erase(b);
 		body_owner.free(p_rid);
 		memdelete(b);
 	} else if (space_owner.owns(p_rid)) {
@@ -591,7 +592,7 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 			d.space = space->handle;
 			d.mode = (uint32_t)b->mode;
 			d.shape = sh;
-			d.flags = b->can_sleep ? 1 : 0;
+			d.flags = (b->can_sleep ? 1 : 0) | (b->ccd ? 2 : 0);
 			_xf_to_floats(b->xf, d.xf);
 			_xf_to_floats(b->shape_xf, d.shape_xf);
 			d.linvel[0] = b->linvel.x; d.linvel[1] = b->linvel.y; d.linvel[2] = b->linvel.z;
@@ -644,11 +645,54 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 	}
 }
 
+void BradotPhysicsServerCUDA::body_set_enable_continuous_collision_detection(RID p_body, bool p_enable) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	ERR_FAIL_COND_MSG(body->slot >= 0, "BradotPhysicsCUDA: continuous collision detection is fixed once the body is in a space (bulk upload).");
+	body->ccd = p_enable;
+}
+
+bool BradotPhysicsServerCUDA::body_is_continuous_collision_detection_enabled(RID p_body) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, false);
+	return body->ccd;
+}
+
+// body_apply_central_force / body_apply_torque (bradot_physics_server_3d.cpp:859-897): accumulated on the host, handed to
+// the GPU as one BPC_FIELD_APPLIED_FORCE row per pushed body before the step (a non-zero row wakes the body there)
+void BradotPhysicsServerCUDA::body_apply_central_force(RID p_body, const Vector3 &p_force) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	if (body->applied_force == Vector3() && body->applied_torque == Vector3()) {
+		pushed_bodies.push_back(body);
+	}
+	body->applied_force += p_force;
+}
+
+void BradotPhysicsServerCUDA::body_apply_torque(RID p_body, const Vector3 &p_torque) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	if (body->applied_force == Vector3() && body->applied_torque == Vector3()) {
+		pushed_bodies.push_back(body);
+	}
+	body->applied_torque += p_torque;
+}
+
 void BradotPhysicsServerCUDA::step(real_t p_step) {
 	if (!active || !ctx) {
 		return;
 	}
 	_flush_pending();
+	for (Body *b : pushed_bodies) {
+		if (b->slot >= 0) {
+			float f[6] = { (float)b->applied_force.x, (float)b->applied_force.y, (float)b->applied_force.z,
+				(float)b->applied_torque.x, (float)b->applied_torque.y, (float)b->applied_torque.z };
+			bpc_bodies_write(ctx, BPC_FIELD_APPLIED_FORCE, b->slot, 1, f);
+		}
+		b->applied_force = Vector3();
+		b->applied_torque = Vector3();
+	}
+	pushed_bodies.clear();
 	ERR_FAIL_COND_MSG(bpc_step(ctx, p_step) < 0, bpc_last_error(ctx));
 }
 

@@ -64,6 +64,8 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		real_t mass = 1, friction = 1, bounce = 0, gravity_scale = 1, lin_damp = 0, ang_damp = 0;
 		uint32_t layer = 1, mask = 1;
 		bool can_sleep = true;
+		bool ccd = false;
+		Vector3 applied_force, applied_torque; // accumulated by body_apply_*, handed over at the next step
 		int slot = -1; // bpc body index once uploaded
 	};
 	struct Joint {
@@ -85,6 +87,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	LocalVector<Body *> pending_bodies;
 	LocalVector<Body *> body_of_slot; // bpc body index -> body (what a query result is mapped back through)
 	LocalVector<Joint *> pending_joints;
+	LocalVector<Body *> pushed_bodies; // bodies with a non-zero applied force / torque for the next step
 	bpc_stats last_stats = {};
 
 	int _shape_handle(Shape *p_shape);
@@ -126,6 +129,10 @@ public:
 	virtual Variant body_get_param(RID p_body, BodyParameter p_param) const override;
 	virtual void body_set_state(RID p_body, BodyState p_state, const Variant &p_variant) override;
 	virtual Variant body_get_state(RID p_body, BodyState p_state) const override;
+	virtual void body_set_enable_continuous_collision_detection(RID p_body, bool p_enable) override;
+	virtual bool body_is_continuous_collision_detection_enabled(RID p_body) const override;
+	virtual void body_apply_central_force(RID p_body, const Vector3 &p_force) override;
+	virtual void body_apply_torque(RID p_body, const Vector3 &p_torque) override;
 	// joints
 	virtual RID joint_create() override;
 	virtual void joint_clear(RID p_joint) override;

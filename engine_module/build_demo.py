@@ -17,7 +17,8 @@ MINE = ["world_boundary_shape_create", "sphere_shape_create", "box_shape_create"
         "shape_set_data", "shape_get_type", "shape_get_data", "space_create", "space_set_active", "space_is_active", "space_set_param",
         "space_get_param", "space_get_direct_state", "body_create", "body_set_space", "body_get_space", "body_set_mode", "body_get_mode", "body_add_shape",
         "body_get_shape_count", "body_set_collision_layer", "body_get_collision_layer", "body_set_collision_mask", "body_get_collision_mask",
-        "body_set_param", "body_get_param", "body_set_state", "body_get_state", "joint_create", "joint_clear", "joint_make_pin",
+        "body_set_param", "body_get_param", "body_set_state", "body_get_state", "body_set_enable_continuous_collision_detection",
+        "body_is_continuous_collision_detection_enabled", "body_apply_central_force", "body_apply_torque", "joint_create", "joint_clear", "joint_make_pin",
         "joint_make_hinge", "joint_disable_collisions_between_bodies", "joint_get_type", "free", "set_active", "init", "step", "sync",
         "flush_queries", "end_sync", "finish", "is_flushing_queries", "get_process_info"]
 

@@ -144,9 +144,22 @@ int main(int argc, char **argv) {
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(b.angvel[0], b.angvel[1], b.angvel[2]));
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, (b.flags & 1) != 0);
+		if (b.flags & 2) {
+			ps->body_set_enable_continuous_collision_detection(body, true);
+		}
 		ps->body_set_space(body, space_r[b.space]);
 		body_r.push_back(body);
 	}
+	// scene flag bit3: pushed before every step, the same push as oracle/ref_harness.cpp push_bodies()
+	auto push = [&]() {
+		for (size_t i = 0; i < body_r.size(); i++) {
+			if (bodies[i].flags & 8) {
+				ps->body_apply_central_force(body_r[i], Vector3(0.5f * (float)((int)(i % 3) - 1), 2.0f, 0.3f));
+				ps->body_apply_torque(body_r[i], Vector3(0.1f, 0.0f, 0.05f * (float)(i % 2)));
+			}
+		}
+	};
+	push();
 	ps->step(hd.dt); // uploads the bodies; joints need uploaded bodies, so they are made after the first tick here
 	for (const ScnJoint &j : joints) {
 		RID jr = ps->joint_create();
@@ -163,6 +176,7 @@ int main(int argc, char **argv) {
 		ps->sync();
 		ps->flush_queries();
 		ps->end_sync();
+		push();
 		ps->step(hd.dt);
 	}
 	ps->sync();
