@@ -8,7 +8,7 @@
 //   modules/bradot_physics_3d/bradot_step_3d.cpp:347-349       parallel _setup_constraint over all constraints
 #include "np_convex_warp.cuh"
 
-#define NP_THREADS 64
+#define NP_THREADS 128 // 128 measured 5 % faster than 64 on the settled C3 pile (72 registers instead of 96)
 
 struct NpArgs {
     uint32_t n_pairs;
