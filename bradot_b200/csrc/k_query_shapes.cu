@@ -122,6 +122,89 @@ __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
     a.counts[r] = cc;
 }
 
+// collide_shape (bradot_space_3d.cpp:383-431): the contact pairs (point on the query shape, point on the body) of every
+// overlapped body, through the reference's collecting callback (append, or replace the least deep once max is reached).
+#define QS_MAX_PAIRS 32
+struct QcArgs {
+    QsArgs q;
+    float *points; // n x max_results x 6
+};
+
+__device__ inline void qc_candidate(const QsArgs &a, uint32_t j, const Sh &qs, const X3 &qx, RawSink &sink) {
+    uint4 m = a.meta[j];
+    if (m.w != a.space || !(m.y & a.mask)) return;
+    BodyXf bx = a.xf[j];
+    X3 xb(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
+    if (!((m.x >> 8) & BF_SHAPE_IDENT)) {
+        BodyXf sx = a.shape_xf[j];
+        xb = xb * X3(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+    }
+    Sh sb = qs_shape(a, m.x >> 24, a.shape_p[j]);
+    Manifold *none = nullptr;
+    solve_static<false>(qs, qx, sb, xb, *none, nullptr, &sink);
+}
+
+__global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
+    const QsArgs &a = c.q;
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= a.n) return;
+    const ShapeRec sr = a.shapes[a.shape_ids[r]];
+    float4 p = sr.p;
+    if (sr.meta.x == SH_CONVEX) p.x = __uint_as_float(sr.meta.y);
+    Sh qs = qs_shape(a, sr.meta.x, p);
+    const float *f = a.xforms + (size_t)r * 12;
+    X3 qx(M3(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8])), V3(f[9], f[10], f[11]));
+    Box3 la;
+    la.pos = f4v(sr.aabb_pos);
+    la.size = f4v(sr.aabb_size);
+    Box3 box = xform_aabb(qx, la);
+    const float grow = 1e-4f;
+    V3 qmin = box.pos - V3(grow, grow, grow), qmax = box.pos + box.size + V3(grow, grow, grow);
+    V3 pts[QS_MAX_PAIRS * 2];
+    RawSink sink;
+    sink.pts = pts;
+    sink.n = 0;
+    sink.max = (int)a.max_results;
+    for (uint32_t k = a.big_start[a.space], ke = a.big_start[a.space + 1]; k < ke; k++) qc_candidate(a, a.big[k], qs, qx, sink);
+    if (a.n_tree == 1) {
+        qc_candidate(a, __float_as_uint(a.leaf_min[0].w), qs, qx, sink);
+    } else if (a.n_tree > 1) {
+        uint32_t stack[96];
+        int sp = 0;
+        uint32_t node = 0;
+        while (true) {
+            const float4 *nd = a.nodes + (size_t)node * 4;
+            float4 lmin = nd[0], lmax = nd[1], rmin = nd[2], rmax = nd[3];
+            uint32_t child[2] = { __float_as_uint(lmin.w), __float_as_uint(rmin.w) };
+            uint32_t srange[2] = { __float_as_uint(lmax.w), __float_as_uint(rmax.w) };
+            bool hit[2];
+            hit[0] = a.space >= (srange[0] & 0xffffu) && a.space <= (srange[0] >> 16) &&
+                     !(lmin.x > qmax.x || lmin.y > qmax.y || lmin.z > qmax.z || qmin.x > lmax.x || qmin.y > lmax.y || qmin.z > lmax.z);
+            hit[1] = a.space >= (srange[1] & 0xffffu) && a.space <= (srange[1] >> 16) &&
+                     !(rmin.x > qmax.x || rmin.y > qmax.y || rmin.z > qmax.z || qmin.x > rmax.x || qmin.y > rmax.y || qmin.z > rmax.z);
+            for (int side = 0; side < 2; side++) {
+                if (hit[side] && (child[side] & QS_LEAF_BIT)) qc_candidate(a, __float_as_uint(a.leaf_min[child[side] & ~QS_LEAF_BIT].w), qs, qx, sink);
+            }
+            bool il = hit[0] && !(child[0] & QS_LEAF_BIT), ir = hit[1] && !(child[1] & QS_LEAF_BIT);
+            if (il) {
+                if (ir && sp < 96) stack[sp++] = child[1];
+                node = child[0];
+            } else if (ir) {
+                node = child[1];
+            } else {
+                if (sp == 0) break;
+                node = stack[--sp];
+            }
+        }
+    }
+    a.counts[r] = sink.n;
+    float *o = c.points + (size_t)r * a.max_results * 6;
+    for (int i = 0; i < sink.n; i++) {
+        o[i * 6 + 0] = pts[i * 2].x; o[i * 6 + 1] = pts[i * 2].y; o[i * 6 + 2] = pts[i * 2].z;
+        o[i * 6 + 3] = pts[i * 2 + 1].x; o[i * 6 + 4] = pts[i * 2 + 1].y; o[i * 6 + 5] = pts[i * 2 + 1].z;
+    }
+}
+
 extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
                                           int max_results, int32_t *out_counts, int32_t *out_bodies) {
     if (!ctx) return -1;
@@ -184,6 +267,74 @@ extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, co
     BPC_CHECK(cudaGetLastError());
     BPC_CHECK(cudaMemcpyAsync(out_counts, a.counts, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     BPC_CHECK(cudaMemcpyAsync(out_bodies, a.bodies, body_words * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int bpc_space_collide_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
+                                        int max_results, int32_t *out_counts, float *out_points) {
+    if (!ctx) return -1;
+    if (space < 0 || (size_t)space >= ctx->spaces.size()) {
+        ctx->err = "bpc_space_collide_shapes: no such space";
+        return -1;
+    }
+    if (n < 0 || max_results < 1 || max_results > QS_MAX_PAIRS || (n > 0 && (!shapes || !xforms || !out_counts || !out_points))) {
+        ctx->err = "bpc_space_collide_shapes: bad arguments (at most 32 contact pairs per query)";
+        return -1;
+    }
+    for (int i = 0; i < n; i++) {
+        if (shapes[i] < 0 || (size_t)shapes[i] >= ctx->h_shapes.size() || ctx->h_shapes[shapes[i]].meta.x == SH_PLANE) {
+            ctx->err = "bpc_space_collide_shapes: invalid query shape (world boundaries cannot be query shapes)";
+            return -1;
+        }
+    }
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (bpc_flush_tables(ctx)) return -1;
+    if (bpc_build_tree(ctx)) return -1;
+    size_t id_words = ((size_t)n + 3) & ~(size_t)3, xf_words = (size_t)n * 12, pt_words = (size_t)n * max_results * 6;
+    ctx->staging.reserve(id_words * 2 + xf_words + pt_words + 16, false, st);
+    if (!ctx->staging.p) {
+        ctx->err = "bpc_space_collide_shapes: out of device memory";
+        return -1;
+    }
+    QcArgs c;
+    QsArgs &a = c.q;
+    a.n = (uint32_t)n;
+    a.n_tree = ctx->n_tree;
+    a.space = (uint32_t)space;
+    a.mask = collision_mask;
+    a.max_results = (uint32_t)max_results;
+    int32_t *d_ids = (int32_t *)ctx->staging.p;
+    float *d_xf = ctx->staging.p + id_words;
+    a.shape_ids = d_ids;
+    a.xforms = d_xf;
+    a.counts = (int32_t *)(ctx->staging.p + id_words + xf_words);
+    a.bodies = nullptr;
+    c.points = ctx->staging.p + id_words * 2 + xf_words;
+    a.shapes = ctx->shapes.p;
+    a.nodes = ctx->nodes.p;
+    a.leaf_min = ctx->leaf_min.p;
+    a.meta = ctx->meta.p;
+    a.xf = ctx->xf.p;
+    a.shape_xf = ctx->shape_xf.p;
+    a.shape_p = ctx->shape_p.p;
+    a.meshes = ctx->meshes.p;
+    a.mverts = ctx->mverts.p;
+    a.mplanes = ctx->mplanes.p;
+    a.medges = ctx->medges.p;
+    a.mfaces = ctx->mfaces.p;
+    a.mindex = ctx->mindex.p;
+    a.big = ctx->big_items.p;
+    a.big_start = ctx->big_start.p;
+    BPC_CHECK(cudaMemcpyAsync(d_ids, shapes, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    BPC_CHECK(cudaMemcpyAsync(d_xf, xforms, xf_words * sizeof(float), cudaMemcpyHostToDevice, st));
+    BPC_CHECK(cudaMemsetAsync(c.points, 0, pt_words * sizeof(float), st));
+    k_collide_shapes<<<(n + QS_THREADS - 1) / QS_THREADS, QS_THREADS, 0, st>>>(c);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaMemcpyAsync(out_counts, a.counts, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaMemcpyAsync(out_points, c.points, pt_words * sizeof(float), cudaMemcpyDeviceToHost, st));
     BPC_CHECK(cudaStreamSynchronize(st));
     return 0;
 }

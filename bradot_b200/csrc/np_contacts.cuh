@@ -106,14 +106,48 @@ __device__ inline void manifold_validate(Manifold &m, float max_sep) {
 
 // _CollectorCallback: the normal handed to the pair callback is ignored there (it is rebuilt from
 // the two points), so only the A/B swap matters.
+// Where a query (collide_shape) wants the raw contact pairs instead of a manifold:
+// BradotPhysicsServer3D::_shape_col_cbk (bradot_physics_server_3d.cpp:1735-1766) -- append, or replace the least deep
+struct RawSink {
+    V3 *pts; // pairs: point on A, point on B
+    int n, max;
+};
+__device__ inline void raw_add(RawSink &r, V3 pA, V3 pB) {
+    if (r.max == 0) return;
+    if (r.n == r.max) {
+        float min_depth = 1e20f;
+        int min_idx = 0;
+        for (int i = 0; i < r.n; i++) {
+            float d = distance_squared(r.pts[i * 2], r.pts[i * 2 + 1]);
+            if (d < min_depth) {
+                min_depth = d;
+                min_idx = i;
+            }
+        }
+        if (distance_squared(pA, pB) < min_depth) return;
+        r.pts[min_idx * 2] = pA;
+        r.pts[min_idx * 2 + 1] = pB;
+    } else {
+        r.pts[r.n * 2] = pA;
+        r.pts[r.n * 2 + 1] = pB;
+        r.n++;
+    }
+}
+
 struct Collector {
     Manifold *m;
+    RawSink *raw = nullptr;
     bool swap;
     bool collided;
     V3 normal;
     V3 *prev_axis;
     __device__ __forceinline__ void call(V3 pA, V3 pB) {
-        if (swap) manifold_add(*m, pB, pA);
+        if (swap) {
+            V3 t = pA;
+            pA = pB;
+            pB = t;
+        }
+        if (raw) raw_add(*raw, pA, pB);
         else manifold_add(*m, pA, pB);
     }
 };

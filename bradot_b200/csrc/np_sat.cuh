@@ -410,17 +410,18 @@ __device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, 
         found = true;
         if (TEST) return true;
         V3 sa = pl_project(p, s);
-        if (swap_result) manifold_add(*c.m, s, sa);
-        else manifold_add(*c.m, sa, s);
+        c.swap = swap_result;
+        c.call(sa, s);
     }
     return found;
 }
 
 // BradotCollisionSolver3D::solve_static (…collision_solver_3d.cpp:362-435) + sat_calculate_penetration dispatch (…sat.cpp:2296-2421)
 template <bool TEST>
-__device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, const X3 &xb, Manifold &m, V3 *sep_axis) {
+__device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, const X3 &xb, Manifold &m, V3 *sep_axis, RawSink *raw = nullptr) {
     Collector c;
     c.m = &m;
+    c.raw = raw;
     c.swap = false;
     c.collided = false;
     c.prev_axis = sep_axis;

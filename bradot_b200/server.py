@@ -37,7 +37,7 @@ EXPORTS = [
     "bpc_shape_create", "bpc_shape_create_convex", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
     "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
-    "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes",
+    "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
 
@@ -80,6 +80,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
     lib.bpc_space_intersect_points.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp, vp]
     lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, ci, vp, vp]
+    lib.bpc_space_collide_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, ci, vp, vp]
     lib.bpc_synchronize.argtypes = [vp]
     lib.bpc_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
     lib.bpc_pair_count.argtypes = [vp]
@@ -261,6 +262,16 @@ class PhysicsServerCUDA:
         self._check(self.lib.bpc_space_intersect_shapes(self.ctx, int(space), len(sh), _ptr(sh), _ptr(xf), ctypes.c_uint(collision_mask),
                                                         int(max_results), _ptr(counts), _ptr(bodies)))
         return counts, bodies
+
+    def collide_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=16):
+        """Batched PhysicsDirectSpaceState3D.collide_shape: (counts int32[n], points float32[n, max_results, 2, 3])."""
+        sh = np.ascontiguousarray(shapes, np.int32).reshape(-1)
+        xf = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
+        counts = np.zeros(len(sh), np.int32)
+        pts = np.zeros((len(sh), max_results, 2, 3), np.float32)
+        self._check(self.lib.bpc_space_collide_shapes(self.ctx, int(space), len(sh), _ptr(sh), _ptr(xf), ctypes.c_uint(collision_mask),
+                                                      int(max_results), _ptr(counts), _ptr(pts)))
+        return counts, pts
 
     def set_solve_order(self, order):
         o = np.ascontiguousarray(order, np.int32).reshape(-1, 3)

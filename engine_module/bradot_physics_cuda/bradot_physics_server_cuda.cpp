@@ -250,6 +250,33 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_
 	return cc;
 }
 
+bool BradotPhysicsDirectSpaceStateCUDA::collide_shape(const ShapeParameters &p_parameters, Vector3 *r_results, int p_result_max, int &r_result_count) {
+	r_result_count = 0;
+	ERR_FAIL_NULL_V(server, false);
+	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.margin != 0.0, false,
+			"BradotPhysicsCUDA: collide_shape with exclude lists, areas or a margin is not supported yet.");
+	if (p_result_max <= 0 || !r_results || !p_parameters.collide_with_bodies) {
+		return false;
+	}
+	BradotPhysicsServerCUDA::Shape *shape = server->shape_owner.get_or_null(p_parameters.shape_rid);
+	ERR_FAIL_NULL_V(shape, false);
+	int32_t handle = server->_shape_handle(shape);
+	ERR_FAIL_COND_V(handle < 0, false);
+	server->_flush_pending();
+	int max_r = p_result_max > 32 ? 32 : p_result_max;
+	float f[12];
+	_xf_to_floats(p_parameters.transform, f);
+	int32_t count = 0;
+	LocalVector<float> pts;
+	pts.resize(max_r * 6);
+	ERR_FAIL_COND_V_MSG(bpc_space_collide_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, max_r, &count, pts.ptr()) < 0, false, bpc_last_error(server->ctx));
+	for (int i = 0; i < count * 2; i++) {
+		r_results[i] = Vector3(pts[i * 3 + 0], pts[i * 3 + 1], pts[i * 3 + 2]);
+	}
+	r_result_count = count;
+	return count > 0;
+}
+
 bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_parameters, RayResult &r_result) {
 	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.pick_ray, false,
 			"BradotPhysicsCUDA: intersect_ray with exclude lists, areas or pick_ray is not supported yet.");

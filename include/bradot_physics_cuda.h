@@ -171,6 +171,13 @@ int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *
 int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
                                int max_results, int32_t *out_counts, int32_t *out_bodies);
 
+/* PhysicsDirectSpaceState3D::collide_shape (servers/physics_server_3d.h; implementation
+ * modules/bradot_physics_3d/bradot_space_3d.cpp:383-431), batched, margin 0: for each query shape the contact pairs with
+ * the bodies it overlaps.  out_points: n x max_results x 6 (point on the query shape, point on the body), max_results <= 32;
+ * once full, a deeper pair replaces the least deep one (the reference's collecting callback). */
+int bpc_space_collide_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
+                             int max_results, int32_t *out_counts, float *out_points);
+
 /* ---- utilities exposed for tests and tools */
 /* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */
 int bpc_sort_u64(bpc_context *ctx, const uint64_t *keys_in, uint64_t *keys_out, int n);

@@ -384,6 +384,28 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 		}
 		put3(sxf, sp.transform.origin);
 	}
+	// collide_shape (bradot_space_3d.cpp:383-431) with the same shapes and poses, up to 16 contact pairs each
+	std::vector<float> cs(n * (1 + 16 * 6), 0.f);
+	for (size_t i = 0; i < n; i++) {
+		PhysicsDirectSpaceState3D::ShapeParameters sp;
+		sp.shape_rid = qshape[i % 3];
+		const float *f = &sxf[i * 12];
+		sp.transform = xf_from(f); // rows, as dumped
+		sp.collision_mask = 0xffffffffu;
+		Vector3 res[32];
+		int cnt = 0;
+		if (ds) {
+			ds->collide_shape(sp, res, 16, cnt);
+		}
+		float *o = &cs[i * (1 + 16 * 6)];
+		o[0] = (float)cnt;
+		for (int k = 0; k < cnt * 2; k++) {
+			o[1 + k * 3 + 0] = res[k].x;
+			o[1 + k * 3 + 1] = res[k].y;
+			o[1 + k * 3 + 2] = res[k].z;
+		}
+	}
+	d.arr("shape_collide", step, "f4", { (uint64_t)n, 1 + 16 * 6 }, cs.data(), cs.size() * 4);
 	d.arr("shape_queries", step, "i4", { (uint64_t)n, 9 }, sq.data(), sq.size() * 4);
 	d.arr("shape_query_xf", step, "f4", { (uint64_t)n, 12 }, sxf.data(), sxf.size() * 4);
 }

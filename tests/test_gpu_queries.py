@@ -132,3 +132,39 @@ def test_intersect_shapes_against_the_reference():
             assert differ <= len(rays) // 1000, (k, differ)     # a shape touching within rounding may flip
         assert overlaps > 1500
         ps.finish()
+
+
+def test_collide_shapes_against_the_reference():
+    """collide_shape: the contact pairs (point on the query shape, point on the body) for the same query shapes and poses."""
+    parity_needed()
+    sc = scenes.mixed_pile(5, half=3.5)
+    rays = _rays(2000, 21, 3.4, 4.0)
+    _, dump = parity.run_oracle(sc, 60, dump_from=0, dump_every=1, rays=rays)
+    ps = parity.new_server(sc, dump)
+    handles = np.array([ps.sphere_shape_create(0.35), ps.box_shape_create((0.3, 0.2, 0.25)), ps.capsule_shape_create(0.2, 0.9)], np.int32)
+    shape_of = handles[np.arange(len(rays)) % 3]
+    pairs_seen = 0
+    for k in (1, 30, 59):
+        parity.load_state(ps, dump, k)
+        counts, pts = ps.collide_shapes(shape_of, dump[("shape_query_xf", k)], max_results=16)
+        ref = dump[("shape_collide", k)]
+        differ = 0
+        for i in range(len(rays)):
+            rc = int(ref[i, 0])
+            if rc >= 16 or counts[i] >= 16:
+                continue                      # which pairs survive a full list depends on the order of the candidates
+            if rc != counts[i]:
+                differ += 1
+                continue
+            if rc == 0:
+                continue
+            a = pts[i, :rc].reshape(rc, 6)
+            b = ref[i, 1:1 + rc * 6].reshape(rc, 6)
+            # same set of pairs (the candidates come in a different order): match each reference pair to its nearest
+            dist = np.abs(a[:, None, :] - b[None, :, :]).max(axis=2)
+            if dist.min(axis=0).max() > 1e-4 or dist.min(axis=1).max() > 1e-4:
+                differ += 1
+            pairs_seen += rc
+        assert differ <= len(rays) // 500, (k, differ)
+    assert pairs_seen > 1000
+    ps.finish()
