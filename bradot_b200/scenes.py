@@ -24,8 +24,17 @@ BODY_DT = np.dtype([
     ("xf", "<f4", 12), ("shape_xf", "<f4", 12), ("linvel", "<f4", 3), ("angvel", "<f4", 3),
     ("mass", "<f4"), ("friction", "<f4"), ("bounce", "<f4"), ("gravity_scale", "<f4"),
     ("lin_damp", "<f4"), ("ang_damp", "<f4"), ("layer", "<u4"), ("mask", "<u4")])
+# joint flags: bit0 the two bodies do not collide, bit1 hinge use_limit, bit2 hinge enable_motor, bit3 `params` given
+# params: pin = PinJointParam order (bias, damping, impulse clamp); hinge = HingeJointParam order (bias, limit upper, limit
+# lower, limit bias, limit softness, limit relaxation, motor target velocity, motor max impulse); priority 0 = default (1)
 JOINT_DT = np.dtype([("type", "<u4"), ("body_a", "<u4"), ("body_b", "<u4"), ("flags", "<u4"),
-                     ("fa", "<f4", 12), ("fb", "<f4", 12)])
+                     ("fa", "<f4", 12), ("fb", "<f4", 12), ("params", "<f4", 8), ("priority", "<u4"), ("pad", "<u4", 3)])
+JOINT_NO_COLLIDE, JOINT_USE_LIMIT, JOINT_ENABLE_MOTOR, JOINT_HAS_PARAMS = 1, 2, 4, 8
+PIN_DEFAULTS = np.array([0.3, 1.0, 0.0, 0, 0, 0, 0, 0], np.float32)
+HINGE_DEFAULTS = np.array([0.3, -np.pi, np.pi, 0.3, 0.9, 1.0, 0.0, 0.0], np.float32)   # upper = -pi, lower = pi: the reference's "no limit"
+# body flags: bit0 can_sleep, bit1 continuous cd, bit2 start asleep, bit3 pushed every step, bit4 / bit5 linear / angular damp
+# mode REPLACE, bits 8..13 axis locks (PhysicsServer3D::BodyAxis: linear x y z, angular x y z)
+BODY_LIN_DAMP_REPLACE, BODY_ANG_DAMP_REPLACE, BODY_LOCK_SHIFT = 16, 32, 8
 IDENT12 = np.array([1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0], dtype=np.float32)
 
 
@@ -90,7 +99,7 @@ class Scene:
 
     # -- file I/O ---------------------------------------------------------------
     def write(self, path):
-        hdr = struct.pack("<4sIIIIIIfI7I", b"BSCN", 1, self.n_spaces, len(self.shapes), len(self.bodies),
+        hdr = struct.pack("<4sIIIIIIfI7I", b"BSCN", 2, self.n_spaces, len(self.shapes), len(self.bodies),
                           len(self.joints), len(self.verts), float(self.dt), self.iterations, *([0] * 7))
         with open(path, "wb") as f:
             f.write(hdr)
@@ -104,7 +113,7 @@ class Scene:
         with open(path, "rb") as f:
             raw = f.read()
         magic, ver, nsp, nsh, nb, nj, nv, dt, it = struct.unpack_from("<4sIIIIIIfI", raw, 0)
-        assert magic == b"BSCN" and ver == 1
+        assert magic == b"BSCN" and ver == 2
         off = struct.calcsize("<4sIIIIIIfI7I")
         sc = Scene(nsp, dt, it)
         sc.shapes = np.frombuffer(raw, SHAPE_DT, nsh, off).copy()

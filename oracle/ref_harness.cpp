@@ -15,7 +15,14 @@
 //   rays.bin: uint32 n, then n x (from xyz, to xyz) float32; every dumped step also holds "rays" (n,8): hit, body
 //   index, position xyz, normal xyz of PhysicsDirectSpaceState3D::intersect_ray in space 0 (mask 0xffffffff), and
 //   "points" (n,9): count and up to 8 body indices of intersect_point at each ray's origin
-//                    [--threads T] [--warmup W] [--quiet]
+//                    [--threads T] [--warmup W] [--state state.bin] [--events events.bin]
+//   state.bin: uint32 n_bodies, then n x 18 float32 (transform rows + origin, linear velocity, angular velocity): applied
+//   to every non-static body through body_set_state after the scene is built (a settled state handed over by the other
+//   side, so that the CPU run does not pay for settling it again).
+//   events.bin: uint32 n, then n x (int32 step, int32 body, int32 kind, float32[12]): applied before the step of that
+//   number.  kind 0 body_set_state(TRANSFORM), 1 LINEAR_VELOCITY, 2 ANGULAR_VELOCITY, 3 free(body), 4 SLEEPING(v[0] != 0).
+// Scenes with several spaces are stepped space by space with the reference's own stepper (what BradotPhysicsServer3D::step
+// does, bradot_physics_server_3d.cpp:1632-1648) whenever a dump is written, so that each space's sweep order can be recorded.
 // Timing JSON goes to stdout (one line).
 
 #include "core/config/engine.h"
@@ -57,7 +64,7 @@ public:
 #pragma pack(push, 1)
 struct ScnHeader {
 	char magic[4]; // "BSCN"
-	uint32_t version; // 1
+	uint32_t version; // 2
 	uint32_t n_spaces, n_shapes, n_bodies, n_joints, n_verts;
 	float dt;
 	uint32_t iterations;
@@ -70,7 +77,9 @@ struct ScnShape {
 	uint32_t pad;
 };
 struct ScnBody {
-	uint32_t space, mode, shape, flags; // flags bit0 can_sleep, bit1 ccd, bit2 start asleep, bit3 pushed every step (see push_bodies)
+	// flags bit0 can_sleep, bit1 ccd, bit2 start asleep, bit3 pushed every step (see push_bodies),
+	// bit4 / bit5 linear / angular damp mode REPLACE, bits 8..13 axis locks (PhysicsServer3D::BodyAxis)
+	uint32_t space, mode, shape, flags;
 	float xf[12]; // basis rows (9) + origin
 	float shape_xf[12];
 	float linvel[3], angvel[3];
@@ -81,6 +90,15 @@ struct ScnJoint {
 	uint32_t type; // 0 pin, 1 hinge
 	uint32_t body_a, body_b, flags; // bit0 disable collisions between bodies
 	float fa[12], fb[12]; // pin: origin of fa/fb only; hinge: local frames
+	// flags bit1: hinge use_limit, bit2: hinge enable_motor, bit3: params are given (else the reference defaults stay)
+	// pin: params[0..2] = PinJointParam bias, damping, impulse clamp; hinge: params[0..7] = HingeJointParam order
+	float params[8];
+	uint32_t priority; // joint_set_solver_priority (0 = leave the default 1)
+	uint32_t pad[3];
+};
+struct Event {
+	int32_t step, body, kind;
+	float v[12];
 };
 #pragma pack(pop)
 
@@ -135,7 +153,50 @@ struct World {
 	std::vector<Vector3> kin_lin;
 	std::vector<float> kin_wy;
 	std::vector<uint32_t> body_flags;
+	std::vector<char> body_freed;
+	// sweep order of the last step, recorded space by space: (island counted over all spaces, constraint)
+	std::vector<std::pair<int, const BradotConstraint3D *>> last_order;
+	int32_t last_stats[4] = { 0, 0, 0, 0 };
+	bool order_valid = false;
 };
+
+// One tick.  With `record`: what BradotPhysicsServer3D::step does (bradot_physics_server_3d.cpp:1632-1648), space by space
+// through the reference's stepper, noting after each space the constraints its islands were solved in.
+static void step_world(World &w, real_t dt, bool record) {
+	BradotPhysicsServer3D *ps = w.ps;
+	if (!record) {
+		ps->step(dt);
+		w.order_valid = false;
+		return;
+	}
+	ps->_update_shapes();
+	ps->island_count = 0;
+	ps->active_objects = 0;
+	ps->collision_pairs = 0;
+	w.last_order.clear();
+	int island_base = 0;
+	for (RID sp : w.spaces) {
+		BradotSpace3D *space = ps->space_owner.get_or_null(sp);
+		if (!ps->active_spaces.has(space)) {
+			continue;
+		}
+		ps->stepper->step(space, dt);
+		ps->island_count += space->get_island_count();
+		ps->active_objects += space->get_active_objects();
+		ps->collision_pairs += space->get_collision_pairs();
+		uint32_t ic = space->get_island_count();
+		for (uint32_t i = 0; i < ic && i < ps->stepper->constraint_islands.size(); i++) {
+			for (BradotConstraint3D *c : ps->stepper->constraint_islands[i]) {
+				w.last_order.push_back({ island_base + (int)i, c });
+			}
+		}
+		island_base += (int)ic;
+	}
+	w.last_stats[0] = ps->island_count;
+	w.last_stats[1] = ps->active_objects;
+	w.last_stats[2] = ps->collision_pairs;
+	w.order_valid = true;
+}
 
 #define PAIR_STRIDE 12
 #define CONTACT_STRIDE 32
@@ -147,6 +208,11 @@ static void dump_step(Dump &d, World &w, int step) {
 	std::vector<float> items;
 	items.reserve(nb * 14);
 	for (int i = 0; i < nb; i++) {
+		if (w.body_freed[i]) { // a freed body keeps its row (all zeros) so that indices stay put
+			bs.insert(bs.end(), 20, 0.f);
+			items.insert(items.end(), 14, 0.f);
+			continue;
+		}
 		BradotBody3D *b = w.body_ptr[i];
 		const Transform3D &t = b->get_transform();
 		for (int r = 0; r < 3; r++) {
@@ -182,6 +248,9 @@ static void dump_step(Dump &d, World &w, int step) {
 	std::vector<float> cf;
 	std::map<const BradotConstraint3D *, int> pair_index;
 	for (int i = 0; i < nb; i++) {
+		if (w.body_freed[i]) {
+			continue;
+		}
 		BradotBody3D *b = w.body_ptr[i];
 		for (const KeyValue<BradotConstraint3D *, int> &E : b->get_constraint_map()) {
 			BradotBodyPair3D *p = dynamic_cast<BradotBodyPair3D *>(E.key);
@@ -226,37 +295,38 @@ static void dump_step(Dump &d, World &w, int step) {
 	d.arr("contacts", step, "f4", { np, 4, CONTACT_STRIDE }, cf.data(), cf.size() * 4);
 
 	// solve order actually used this step: after _pre_solve_island/_solve_island the island vectors
-	// hold the constraints that were solved, in sweep order (bradot_step_3d.cpp:121-160).
+	// hold the constraints that were solved, in sweep order (bradot_step_3d.cpp:121-160); step_world noted them.
 	std::vector<int32_t> order; // (island, kind, index) kind 0 = pair (index into pair_ids), 1 = joint (index into scene joints)
-	BradotStep3D *st = w.ps->stepper;
-	// islands of all spaces are overwritten space by space; only meaningful for single-space scenes
-	if (w.spaces.size() == 1) {
-		BradotSpace3D *space = w.ps->space_owner.get_or_null(w.spaces[0]);
-		uint32_t ic = space->get_island_count();
+	if (w.order_valid) {
 		std::map<const BradotConstraint3D *, int> joint_index;
 		for (size_t j = 0; j < w.joints.size(); j++) {
 			joint_index[w.ps->joint_owner.get_or_null(w.joints[j])] = j;
 		}
-		for (uint32_t i = 0; i < ic && i < st->constraint_islands.size(); i++) {
-			for (BradotConstraint3D *c : st->constraint_islands[i]) {
-				auto it = pair_index.find(c);
-				if (it != pair_index.end()) {
-					order.push_back(i);
-					order.push_back(0);
-					order.push_back(it->second);
-				} else {
-					auto jt = joint_index.find(c);
-					if (jt != joint_index.end()) {
-						order.push_back(i);
-						order.push_back(1);
-						order.push_back(jt->second);
-					}
+		for (const std::pair<int, const BradotConstraint3D *> &oc : w.last_order) {
+			auto it = pair_index.find(oc.second);
+			if (it != pair_index.end()) {
+				order.push_back(oc.first);
+				order.push_back(0);
+				order.push_back(it->second);
+			} else {
+				auto jt = joint_index.find(oc.second);
+				if (jt != joint_index.end()) {
+					order.push_back(oc.first);
+					order.push_back(1);
+					order.push_back(jt->second);
 				}
 			}
 		}
-		int32_t stats[4] = { (int32_t)space->get_island_count(), (int32_t)space->get_active_objects(), (int32_t)space->get_collision_pairs(), 0 };
-		d.arr("stats", step, "i4", { 4 }, stats, sizeof(stats));
+	} else {
+		w.last_stats[0] = w.last_stats[1] = w.last_stats[2] = 0;
+		for (RID sp : w.spaces) {
+			BradotSpace3D *space = w.ps->space_owner.get_or_null(sp);
+			w.last_stats[0] += space->get_island_count();
+			w.last_stats[1] += space->get_active_objects();
+			w.last_stats[2] += space->get_collision_pairs();
+		}
 	}
+	d.arr("stats", step, "i4", { 4 }, w.last_stats, sizeof(w.last_stats));
 	d.arr("solve_order", step, "i4", { (uint64_t)order.size() / 3, 3 }, order.data(), order.size() * 4);
 }
 
@@ -265,7 +335,7 @@ static void dump_step(Dump &d, World &w, int step) {
 // only: F = (0.5 (i % 3 - 1), 2, 0.3) N, T = (0.1, 0, 0.05 (i % 2)) N m.
 static void push_bodies(World &w, const std::vector<uint32_t> &flags) {
 	for (size_t i = 0; i < w.bodies.size(); i++) {
-		if (!(flags[i] & 8)) {
+		if (!(flags[i] & 8) || w.body_freed[i]) {
 			continue;
 		}
 		w.ps->body_apply_central_force(w.bodies[i], Vector3(0.5f * (float)((int)(i % 3) - 1), 2.0f, 0.3f));
@@ -281,6 +351,9 @@ static void drive_kinematic(Dump &d, World &w, int step, float dt, bool dump) {
 	}
 	std::vector<float> out;
 	for (size_t i = 0; i < w.kin_body.size(); i++) {
+		if (w.body_freed[w.kin_body[i]]) {
+			continue;
+		}
 		real_t t = (real_t)step * dt;
 		Transform3D x;
 		x.basis = Basis(Vector3(0, 1, 0), w.kin_wy[i] * t) * w.kin_xf0[i].basis;
@@ -475,7 +548,7 @@ int main(int argc, char **argv) {
 	}
 	const char *scene_path = argv[1];
 	int steps = 1, dump_from = 0, dump_every = 1, threads = -1, warmup = 0;
-	const char *dump_path = nullptr, *rays_path = nullptr;
+	const char *dump_path = nullptr, *rays_path = nullptr, *state_path = nullptr, *events_path = nullptr;
 	for (int i = 2; i < argc; i++) {
 		std::string a = argv[i];
 		if (a == "--steps") {
@@ -492,6 +565,10 @@ int main(int argc, char **argv) {
 			warmup = atoi(argv[++i]);
 		} else if (a == "--rays") {
 			rays_path = argv[++i];
+		} else if (a == "--state") {
+			state_path = argv[++i];
+		} else if (a == "--events") {
+			events_path = argv[++i];
 		}
 	}
 
@@ -516,7 +593,7 @@ int main(int argc, char **argv) {
 		return 2;
 	}
 	ScnHeader hd;
-	if (fread(&hd, sizeof(hd), 1, sf) != 1 || memcmp(hd.magic, "BSCN", 4) != 0) {
+	if (fread(&hd, sizeof(hd), 1, sf) != 1 || memcmp(hd.magic, "BSCN", 4) != 0 || hd.version != 2) {
 		fprintf(stderr, "bad scene file\n");
 		return 2;
 	}
@@ -616,6 +693,17 @@ int main(int argc, char **argv) {
 		if (b.flags & 2) {
 			ps->body_set_enable_continuous_collision_detection(body, true);
 		}
+		if (b.flags & 16) {
+			ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_LINEAR_DAMP_MODE, PhysicsServer3D::BODY_DAMP_MODE_REPLACE);
+		}
+		if (b.flags & 32) {
+			ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_ANGULAR_DAMP_MODE, PhysicsServer3D::BODY_DAMP_MODE_REPLACE);
+		}
+		for (int ax = 0; ax < 6; ax++) {
+			if ((b.flags >> 8) & (1u << ax)) {
+				ps->body_set_axis_lock(body, (PhysicsServer3D::BodyAxis)(1 << ax), true);
+			}
+		}
 		ps->body_set_space(body, w.spaces[b.space]);
 		if (b.flags & 4) {
 			ps->body_set_state(body, PhysicsServer3D::BODY_STATE_SLEEPING, true);
@@ -626,6 +714,7 @@ int main(int argc, char **argv) {
 		w.body_index[bp] = i;
 		w.body_space.push_back(b.space);
 		w.body_flags.push_back(b.flags);
+		w.body_freed.push_back(0);
 		if (b.mode == PhysicsServer3D::BODY_MODE_KINEMATIC) {
 			w.kin_body.push_back(i);
 			w.kin_xf0.push_back(xf_from(b.xf));
@@ -644,7 +733,65 @@ int main(int argc, char **argv) {
 		if (j.flags & 1) {
 			ps->joint_disable_collisions_between_bodies(jr, true);
 		}
+		if (j.flags & 8) {
+			if (j.type == 0) {
+				for (int k = 0; k < 3; k++) {
+					ps->pin_joint_set_param(jr, (PhysicsServer3D::PinJointParam)k, j.params[k]);
+				}
+			} else {
+				for (int k = 0; k < (int)PhysicsServer3D::HINGE_JOINT_MAX; k++) {
+					ps->hinge_joint_set_param(jr, (PhysicsServer3D::HingeJointParam)k, j.params[k]);
+				}
+			}
+		}
+		if (j.type == 1) {
+			ps->hinge_joint_set_flag(jr, PhysicsServer3D::HINGE_JOINT_FLAG_USE_LIMIT, (j.flags & 2) != 0);
+			ps->hinge_joint_set_flag(jr, PhysicsServer3D::HINGE_JOINT_FLAG_ENABLE_MOTOR, (j.flags & 4) != 0);
+		}
+		if (j.priority) {
+			ps->joint_set_solver_priority(jr, (int)j.priority);
+		}
 		w.joints.push_back(jr);
+	}
+
+	// a state handed over by the other side: transforms and velocities of the moving bodies
+	if (state_path) {
+		FILE *stf = fopen(state_path, "rb");
+		uint32_t ns = 0;
+		if (!stf || fread(&ns, 4, 1, stf) != 1 || ns != hd.n_bodies) {
+			fprintf(stderr, "cannot read %s (or its body count differs from the scene's)\n", state_path);
+			return 2;
+		}
+		std::vector<float> stv((size_t)ns * 18);
+		if (fread(stv.data(), 4, stv.size(), stf) != stv.size()) {
+			fprintf(stderr, "short state file\n");
+			return 2;
+		}
+		fclose(stf);
+		for (uint32_t i = 0; i < ns; i++) {
+			if (sbodies[i].mode < PhysicsServer3D::BODY_MODE_RIGID) {
+				continue;
+			}
+			const float *f = &stv[(size_t)i * 18];
+			ps->body_set_state(w.bodies[i], PhysicsServer3D::BODY_STATE_TRANSFORM, xf_from(f));
+			ps->body_set_state(w.bodies[i], PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(f[12], f[13], f[14]));
+			ps->body_set_state(w.bodies[i], PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(f[15], f[16], f[17]));
+		}
+	}
+	std::vector<Event> events;
+	if (events_path) {
+		FILE *ef = fopen(events_path, "rb");
+		uint32_t ne = 0;
+		if (!ef || fread(&ne, 4, 1, ef) != 1) {
+			fprintf(stderr, "cannot read %s\n", events_path);
+			return 2;
+		}
+		events.resize(ne);
+		if (ne && fread(events.data(), sizeof(Event), ne, ef) != ne) {
+			fprintf(stderr, "short events file\n");
+			return 2;
+		}
+		fclose(ef);
 	}
 
 	Dump d;
@@ -668,12 +815,37 @@ int main(int argc, char **argv) {
 	for (int s = 0; s < warmup; s++) {
 		ps->step(hd.dt);
 	}
+	const bool record = d.f != nullptr;
 	double phase_us[5] = { 0, 0, 0, 0, 0 };
 	auto t0 = std::chrono::steady_clock::now();
 	for (int s = 1; s <= steps; s++) {
+		for (const Event &e : events) {
+			if (e.step != s || e.body < 0 || e.body >= (int)w.bodies.size() || w.body_freed[e.body]) {
+				continue;
+			}
+			RID body = w.bodies[e.body];
+			switch (e.kind) {
+				case 0:
+					ps->body_set_state(body, PhysicsServer3D::BODY_STATE_TRANSFORM, xf_from(e.v));
+					break;
+				case 1:
+					ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(e.v[0], e.v[1], e.v[2]));
+					break;
+				case 2:
+					ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(e.v[0], e.v[1], e.v[2]));
+					break;
+				case 3:
+					ps->free(body);
+					w.body_freed[e.body] = 1;
+					break;
+				case 4:
+					ps->body_set_state(body, PhysicsServer3D::BODY_STATE_SLEEPING, e.v[0] != 0.f);
+					break;
+			}
+		}
 		drive_kinematic(d, w, s, hd.dt, true);
 		push_bodies(w, w.body_flags);
-		ps->step(hd.dt);
+		step_world(w, hd.dt, record && s >= dump_from - 1);
 		for (RID sp : w.spaces) {
 			BradotSpace3D *space = ps->space_owner.get_or_null(sp);
 			for (int k = 0; k < 5; k++) {
@@ -691,8 +863,8 @@ int main(int argc, char **argv) {
 		fclose(d.f);
 	}
 	uint64_t active = 0;
-	for (BradotBody3D *b : w.body_ptr) {
-		if (b->get_mode() >= PhysicsServer3D::BODY_MODE_KINEMATIC) {
+	for (size_t i = 0; i < w.body_ptr.size(); i++) {
+		if (!w.body_freed[i] && w.body_ptr[i]->get_mode() >= PhysicsServer3D::BODY_MODE_KINEMATIC) {
 			active++;
 		}
 	}
