@@ -40,7 +40,7 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     ctx->xf.free_(); ctx->shape_xf.free_(); ctx->vel.free_(); ctx->massw.free_(); ctx->props.free_(); ctx->forces.free_();
-    ctx->meta.free_(); ctx->shape_id.free_(); ctx->shape_p.free_(); ctx->np_work.free_(); ctx->np_cwork.free_(); ctx->staging.free_(); ctx->a_range.free_(); ctx->a_range_cur.free_(); ctx->jsetup.free_(); ctx->items.free_(); ctx->npairs.free_(); ctx->tree_items.free_(); ctx->kin.free_(); ctx->kin_ids.free_(); ctx->ccd_ids.free_();
+    ctx->meta.free_(); ctx->io_slots.free_(); ctx->shape_id.free_(); ctx->shape_p.free_(); ctx->np_work.free_(); ctx->np_cwork.free_(); ctx->staging.free_(); ctx->a_range.free_(); ctx->a_range_cur.free_(); ctx->jsetup.free_(); ctx->items.free_(); ctx->npairs.free_(); ctx->tree_items.free_(); ctx->kin.free_(); ctx->kin_ids.free_(); ctx->ccd_ids.free_();
     ctx->island.free_(); ctx->island_flag.free_(); ctx->shapes.free_(); ctx->meshes.free_(); ctx->mverts.free_();
     ctx->mplanes.free_(); ctx->medges.free_(); ctx->mfaces.free_(); ctx->mindex.free_(); ctx->d_spaces.free_();
     ctx->keys.free_(); ctx->keys_alt.free_(); ctx->vals.free_(); ctx->vals_alt.free_(); ctx->hist.free_();
@@ -76,6 +76,7 @@ extern "C" int bpc_space_create(bpc_context *ctx) {
     if (ctx->spaces.size() >= 65535) return fail(ctx, "too many spaces (limit 65535)");
     ctx->spaces.push_back(SpaceParams());
     ctx->spaces_dirty = true;
+    ctx->lists_dirty = true; // per-space offsets of the unbounded statics
     return (int)ctx->spaces.size() - 1;
 }
 
@@ -91,7 +92,10 @@ extern "C" int bpc_space_set_param(bpc_context *ctx, int space, int param, float
         case BPC_SPACE_BODY_LINEAR_VELOCITY_SLEEP_THRESHOLD: s.sleep_lin = v; break;
         case BPC_SPACE_BODY_ANGULAR_VELOCITY_SLEEP_THRESHOLD: s.sleep_ang = v; break;
         case BPC_SPACE_BODY_TIME_TO_SLEEP: s.time_to_sleep = v; break;
-        case BPC_SPACE_SOLVER_ITERATIONS: s.iterations = (int)v; break;
+        case BPC_SPACE_SOLVER_ITERATIONS: // per space; the solver records it in 8 bits per constraint
+            if (!(v >= 1.f && v <= 255.f)) return fail(ctx, "bpc_space_set_param: solver iterations must be 1..255");
+            s.iterations = (int)v;
+            break;
         case BPC_SPACE_GRAVITY_X: s.gravity[0] = v; break;
         case BPC_SPACE_GRAVITY_Y: s.gravity[1] = v; break;
         case BPC_SPACE_GRAVITY_Z: s.gravity[2] = v; break;
@@ -100,6 +104,94 @@ extern "C" int bpc_space_set_param(bpc_context *ctx, int space, int param, float
         default: return fail(ctx, "bpc_space_set_param: unknown parameter");
     }
     ctx->spaces_dirty = true;
+    return 0;
+}
+
+// space_set_active (P3D/bradot_physics_server_3d.cpp:162-170): bodies of an inactive space are frozen -- no stage moves them,
+// their island never counts as awake, so their pairs and cached contacts are carried along untouched
+__global__ void k_freeze_space(uint32_t n, uint32_t space, int freeze, uint4 *__restrict__ meta) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint4 m = meta[i];
+    if (m.w != space || (m.y == 0 && m.z == 0 && (m.x & 0xffu) == MODE_STATIC && ((m.x >> 8) & BF_FROZEN))) return; // other space, or a tombstone
+    uint32_t x = freeze ? (m.x | (BF_FROZEN << 8)) : (m.x & ~(BF_FROZEN << 8));
+    if (x != m.x) meta[i].x = x;
+}
+
+extern "C" int bpc_space_set_active(bpc_context *ctx, int space, int active) {
+    if (!ctx) return -1;
+    if (space < 0 || space >= (int)ctx->spaces.size() || !ctx->spaces[space].alive) return fail(ctx, "bpc_space_set_active: invalid space");
+    SpaceParams &s = ctx->spaces[space];
+    if ((s.active != 0) == (active != 0)) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (bpc_resolve_step(ctx)) return -1;
+    s.active = active ? 1 : 0;
+    ctx->spaces_dirty = true;
+    if (ctx->n_bodies) {
+        k_freeze_space<<<(ctx->n_bodies + 255) / 256, 256, 0, ctx->stream>>>(ctx->n_bodies, (uint32_t)space, !active, ctx->meta.p);
+        BPC_CHECK(cudaGetLastError());
+    }
+    return 0;
+}
+
+extern "C" int bpc_space_destroy(bpc_context *ctx, int space) {
+    if (!ctx) return -1;
+    if (space < 0 || space >= (int)ctx->spaces.size() || !ctx->spaces[space].alive) return fail(ctx, "bpc_space_destroy: invalid space");
+    std::vector<int32_t> slots;
+    for (uint32_t i = 0; i < ctx->n_bodies; i++) {
+        if (!ctx->h_dead[i] && ctx->h_space_of[i] == (uint32_t)space) slots.push_back((int32_t)i);
+    }
+    if (!slots.empty() && bpc_bodies_destroy(ctx, slots.data(), (int)slots.size())) return -1;
+    ctx->spaces[space].alive = 0;
+    ctx->spaces[space].active = 0;
+    ctx->spaces_dirty = true;
+    return 0;
+}
+
+int bpc_ensure_pair_cap(bpc_context *ctx, size_t need);
+
+// Size the buffers of a step for `bodies` bodies and `pairs` broadphase pairs, so that no step below those counts allocates.
+extern "C" int bpc_reserve(bpc_context *ctx, int bodies, int pairs) {
+    if (!ctx) return -1;
+    if (bodies < 0 || pairs < 0) return fail(ctx, "bpc_reserve: negative size");
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    size_t nb = (size_t)bodies, np = (size_t)pairs, nj = ctx->h_joints.size();
+    bool ok = true;
+#define RESERVE(buf, count, keep)                \
+    do {                                         \
+        (buf).reserve((count), (keep), st);      \
+        ok = ok && ((count) == 0 || (buf).p);    \
+    } while (0)
+    if (nb) {
+        RESERVE(ctx->xf, nb, true); RESERVE(ctx->shape_xf, nb, true); RESERVE(ctx->vel, nb, true); RESERVE(ctx->massw, nb, true);
+        RESERVE(ctx->props, nb, true); RESERVE(ctx->forces, nb, true); RESERVE(ctx->meta, nb, true); RESERVE(ctx->shape_id, nb, true);
+        RESERVE(ctx->shape_p, nb, true); RESERVE(ctx->items, nb, true); RESERVE(ctx->npairs, nb, true); RESERVE(ctx->island, nb, true);
+        RESERVE(ctx->island_flag, nb, true);
+        // broadphase tree
+        RESERVE(ctx->leaf_min, nb, false); RESERVE(ctx->leaf_max, nb, false); RESERVE(ctx->nodes, nb * 4, false);
+        RESERVE(ctx->node_parent, nb * 2, false); RESERVE(ctx->node_flag, nb, false); RESERVE(ctx->node_maxleaf, nb * 2, false);
+        RESERVE(ctx->bounds, 2, false); RESERVE(ctx->a_range, nb * 2, false); RESERVE(ctx->a_range_cur, nb * 2, false);
+        RESERVE(ctx->body_best, nb * 2, false); RESERVE(ctx->body_colmask, nb, false);
+        RESERVE(ctx->staging, nb * 19, false);
+    }
+    size_t nk = std::max(nb, np);
+    if (nk) {
+        RESERVE(ctx->keys, nk, false); RESERVE(ctx->keys_alt, nk, false); RESERVE(ctx->vals, nk, false); RESERVE(ctx->vals_alt, nk, false);
+        RESERVE(ctx->hist, (size_t)256 * ((nk + 2047) / 2048) + 256, false);
+    }
+    if (np) {
+        size_t maxc = np + nj + 1;
+        RESERVE(ctx->np_work, np + 1, false);
+        if ((ctx->shape_type_mask >> SH_CONVEX) & 1u) RESERVE(ctx->np_cwork, np + 1, false);
+        RESERVE(ctx->con_list, maxc, false); RESERVE(ctx->con_color, maxc, false); RESERVE(ctx->con_sorted, maxc, false);
+        RESERVE(ctx->con_info, maxc, false); RESERVE(ctx->scontacts, maxc * 4, false);
+        RESERVE(ctx->color_start, 2 * (64 + 4), false);
+        if (ok && bpc_ensure_pair_cap(ctx, np)) return -1;
+    }
+#undef RESERVE
+    if (!ok) return fail(ctx, "bpc_reserve: out of device memory");
+    BPC_CHECK(cudaStreamSynchronize(st));
     return 0;
 }
 
@@ -140,6 +232,17 @@ extern "C" int bpc_shape_create_convex(bpc_context *ctx, const float *verts, int
                                        const int32_t *indices, int ni, const int32_t *edges, int ne) {
     if (!ctx) return -1;
     if (nv <= 0 || nf <= 0 || !verts || !planes || !faces || !indices || (ne > 0 && !edges)) return fail(ctx, "bpc_shape_create_convex: empty mesh");
+    // validate everything first: nothing is appended to the pools unless the whole mesh is sound
+    for (int i = 0; i < nf; i++) {
+        if (faces[2 * i] < 0 || faces[2 * i + 1] < 0 || faces[2 * i] + faces[2 * i + 1] > ni) return fail(ctx, "bpc_shape_create_convex: face index range out of bounds");
+    }
+    for (int i = 0; i < ni; i++) {
+        if (indices[i] < 0 || indices[i] >= nv) return fail(ctx, "bpc_shape_create_convex: vertex index out of bounds");
+    }
+    for (int i = 0; i < ne; i++) {
+        if (edges[4 * i] < 0 || edges[4 * i] >= nv || edges[4 * i + 1] < 0 || edges[4 * i + 1] >= nv) return fail(ctx, "bpc_shape_create_convex: edge vertex out of bounds");
+        if (edges[4 * i + 2] < 0 || edges[4 * i + 2] >= nf || edges[4 * i + 3] < 0 || edges[4 * i + 3] >= nf) return fail(ctx, "bpc_shape_create_convex: edge face out of bounds");
+    }
     MeshRec m;
     m.vert_ofs = (uint32_t)ctx->h_mverts.size();
     m.vert_cnt = (uint32_t)nv;
@@ -164,13 +267,9 @@ extern "C" int bpc_shape_create_convex(bpc_context *ctx, const float *verts, int
     }
     for (int i = 0; i < nf; i++) {
         ctx->h_mplanes.push_back(make_float4(planes[4 * i], planes[4 * i + 1], planes[4 * i + 2], planes[4 * i + 3]));
-        if (faces[2 * i] < 0 || faces[2 * i] + faces[2 * i + 1] > ni) return fail(ctx, "bpc_shape_create_convex: face index range out of bounds");
         ctx->h_mfaces.push_back(make_uint2(m.index_ofs + (uint32_t)faces[2 * i], (uint32_t)faces[2 * i + 1]));
     }
-    for (int i = 0; i < ni; i++) {
-        if (indices[i] < 0 || indices[i] >= nv) return fail(ctx, "bpc_shape_create_convex: vertex index out of bounds");
-        ctx->h_mindex.push_back((uint32_t)indices[i]);
-    }
+    for (int i = 0; i < ni; i++) ctx->h_mindex.push_back((uint32_t)indices[i]);
     for (int i = 0; i < ne; i++) {
         ctx->h_medges.push_back(make_uint4((uint32_t)edges[4 * i], (uint32_t)edges[4 * i + 1], (uint32_t)edges[4 * i + 2], (uint32_t)edges[4 * i + 3]));
     }
@@ -197,6 +296,7 @@ static int upload(bpc_context *ctx, DevBuf<T> &d, const std::vector<T> &h) {
 }
 
 int bpc_flush_tables(bpc_context *ctx) {
+    if (ctx->lists_dirty && bpc_rebuild_lists(ctx)) return -1;
     if (ctx->spaces_dirty) {
         if (upload(ctx, ctx->d_spaces, ctx->spaces)) return -1;
         ctx->spaces_dirty = false;

@@ -9,6 +9,7 @@
 #include "bpc_internal.h"
 
 int bpc_flush_tables(bpc_context *ctx);
+int bpc_resolve_step(bpc_context *ctx);
 
 static int fail(bpc_context *ctx, const char *msg) {
     ctx->err = msg;
@@ -143,52 +144,84 @@ static bool grow(bpc_context *ctx, DevBuf<T> &b, size_t n) {
     return b.p != nullptr;
 }
 
-static int rebuild_item_lists(bpc_context *ctx) {
+// Lists derived from the host mirrors: items of the LBVH, unbounded statics per space, kinematic and CCD bodies.
+int bpc_rebuild_lists(bpc_context *ctx) {
     std::vector<uint32_t> tree, big;
     uint32_t nsp = (uint32_t)ctx->spaces.size();
     std::vector<uint32_t> start(nsp + 1, 0);
+    ctx->h_kin_ids.clear();
+    ctx->h_ccd_ids.clear();
     for (uint32_t i = 0; i < ctx->n_bodies; i++) {
+        if (ctx->h_dead[i]) continue;
         if (ctx->h_big[i]) start[ctx->h_space_of[i] + 1]++;
         else tree.push_back(i);
+        if (ctx->h_mode[i] == MODE_KINEMATIC) ctx->h_kin_ids.push_back(i);
+        if (ctx->h_ccd[i] && ctx->h_mode[i] >= MODE_RIGID) ctx->h_ccd_ids.push_back(i);
     }
     for (uint32_t s = 0; s < nsp; s++) start[s + 1] += start[s];
     big.resize(start[nsp]);
     {
         std::vector<uint32_t> cur(start.begin(), start.end() - 1);
         for (uint32_t i = 0; i < ctx->n_bodies; i++) {
-            if (ctx->h_big[i]) big[cur[ctx->h_space_of[i]]++] = i;
+            if (ctx->h_big[i] && !ctx->h_dead[i]) big[cur[ctx->h_space_of[i]]++] = i;
         }
     }
-    ctx->big_start.reserve(nsp + 1, false, ctx->stream);
-    if (!ctx->big_start.p) return fail(ctx, "out of device memory");
-    BPC_CHECK(cudaMemcpyAsync(ctx->big_start.p, start.data(), (nsp + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
-    ctx->tree_items.reserve(tree.size() + 1, false, ctx->stream);
-    ctx->big_items.reserve(big.size() + 1, false, ctx->stream);
-    if (!ctx->tree_items.p || !ctx->big_items.p) return fail(ctx, "out of device memory");
-    if (!tree.empty()) BPC_CHECK(cudaMemcpyAsync(ctx->tree_items.p, tree.data(), tree.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-    if (!big.empty()) BPC_CHECK(cudaMemcpyAsync(ctx->big_items.p, big.data(), big.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-    BPC_CHECK(cudaStreamSynchronize(ctx->stream));
+    cudaStream_t st = ctx->stream;
+    ctx->big_start.reserve(nsp + 1, false, st);
+    ctx->tree_items.reserve(tree.size() + 1, false, st);
+    ctx->big_items.reserve(big.size() + 1, false, st);
+    ctx->kin_ids.reserve(ctx->h_kin_ids.size() + 1, false, st);
+    ctx->ccd_ids.reserve(ctx->h_ccd_ids.size() + 1, false, st);
+    if (!ctx->big_start.p || !ctx->tree_items.p || !ctx->big_items.p || !ctx->kin_ids.p || !ctx->ccd_ids.p) return fail(ctx, "out of device memory");
+    BPC_CHECK(cudaMemcpyAsync(ctx->big_start.p, start.data(), (nsp + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (!tree.empty()) BPC_CHECK(cudaMemcpyAsync(ctx->tree_items.p, tree.data(), tree.size() * 4, cudaMemcpyHostToDevice, st));
+    if (!big.empty()) BPC_CHECK(cudaMemcpyAsync(ctx->big_items.p, big.data(), big.size() * 4, cudaMemcpyHostToDevice, st));
+    if (!ctx->h_kin_ids.empty()) BPC_CHECK(cudaMemcpyAsync(ctx->kin_ids.p, ctx->h_kin_ids.data(), ctx->h_kin_ids.size() * 4, cudaMemcpyHostToDevice, st));
+    if (!ctx->h_ccd_ids.empty()) BPC_CHECK(cudaMemcpyAsync(ctx->ccd_ids.p, ctx->h_ccd_ids.data(), ctx->h_ccd_ids.size() * 4, cudaMemcpyHostToDevice, st));
+    if (!ctx->h_kin_ids.empty()) {
+        ctx->kin.reserve(ctx->n_bodies, true, st);
+        if (!ctx->kin.p) return fail(ctx, "out of device memory");
+    }
+    BPC_CHECK(cudaStreamSynchronize(st));
     ctx->n_tree = (uint32_t)tree.size();
     ctx->n_big = (uint32_t)big.size();
+    ctx->lists_dirty = false;
     return 0;
 }
 
-extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, int n) {
-    if (!ctx) return -1;
-    if (n <= 0 || !descs) return fail(ctx, "bpc_bodies_create: no bodies given");
-    BPC_CHECK(cudaSetDevice(ctx->device));
-    uint32_t first = ctx->n_bodies;
-    size_t total = (size_t)first + n;
-    for (int i = 0; i < n; i++) {
-        if (descs[i].space >= ctx->spaces.size()) return fail(ctx, "bpc_bodies_create: invalid space");
-        if (descs[i].shape >= ctx->h_shapes.size()) return fail(ctx, "bpc_bodies_create: invalid shape");
-        if (descs[i].mode > MODE_RIGID_LINEAR) return fail(ctx, "bpc_bodies_create: invalid body mode");
+static bool grow_bodies(bpc_context *ctx, size_t total) {
+    return grow(ctx, ctx->xf, total) && grow(ctx, ctx->shape_xf, total) && grow(ctx, ctx->vel, total) && grow(ctx, ctx->massw, total) &&
+           grow(ctx, ctx->props, total) && grow(ctx, ctx->forces, total) && grow(ctx, ctx->meta, total) && grow(ctx, ctx->shape_id, total) &&
+           grow(ctx, ctx->shape_p, total) && grow(ctx, ctx->items, total) && grow(ctx, ctx->npairs, total) && grow(ctx, ctx->island, total) &&
+           grow(ctx, ctx->island_flag, total) && (ctx->kin.p == nullptr || grow(ctx, ctx->kin, total));
+}
+
+// copy host records to the device slots: one copy when the slots are consecutive, else one per slot
+template <typename T>
+static int put(bpc_context *ctx, DevBuf<T> &d, const std::vector<T> &h, const uint32_t *slots, bool consecutive) {
+    size_t n = h.size();
+    if (consecutive) {
+        BPC_CHECK(cudaMemcpyAsync(d.p + slots[0], h.data(), n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    } else {
+        for (size_t i = 0; i < n; i++) BPC_CHECK(cudaMemcpyAsync(d.p + slots[i], &h[i], sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
     }
-    if (!grow(ctx, ctx->xf, total) || !grow(ctx, ctx->shape_xf, total) || !grow(ctx, ctx->vel, total) || !grow(ctx, ctx->massw, total) ||
-        !grow(ctx, ctx->props, total) || !grow(ctx, ctx->forces, total) || !grow(ctx, ctx->meta, total) || !grow(ctx, ctx->shape_id, total) ||
-        !grow(ctx, ctx->shape_p, total) || !grow(ctx, ctx->items, total) || !grow(ctx, ctx->npairs, total) || !grow(ctx, ctx->island, total) || !grow(ctx, ctx->island_flag, total))
-        return fail(ctx, "bpc_bodies_create: out of device memory");
-    if (bpc_flush_tables(ctx)) return -1;
+    return 0;
+}
+
+static int validate_descs(bpc_context *ctx, const bpc_body_desc *descs, int n, const char *who) {
+    for (int i = 0; i < n; i++) {
+        if (descs[i].space >= ctx->spaces.size() || !ctx->spaces[descs[i].space].alive) return fail(ctx, (std::string(who) + ": invalid space").c_str());
+        if (descs[i].shape >= ctx->h_shapes.size()) return fail(ctx, (std::string(who) + ": invalid shape").c_str());
+        if (descs[i].mode > MODE_RIGID_LINEAR) return fail(ctx, (std::string(who) + ": invalid body mode").c_str());
+    }
+    return 0;
+}
+
+// Write `n` body records into the given slots (all < n_bodies, buffers large enough).  keep_state: transform, velocities,
+// sleep state and still time stay what they are on the device.
+static int write_body_slots(bpc_context *ctx, const uint32_t *slots, const bpc_body_desc *descs, int n, bool keep_state) {
+    bool consecutive = true;
+    for (int i = 1; i < n; i++) consecutive = consecutive && slots[i] == slots[0] + (uint32_t)i;
     std::vector<BodyXf> xf(n), sxf(n);
     std::vector<BodyVel> vel(n);
     std::vector<BodyMassW> mw(n);
@@ -196,12 +229,23 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
     std::vector<uint4> meta(n);
     std::vector<uint32_t> sid(n);
     std::vector<float4> sp(n);
-    ctx->h_mode.resize(total);
-    ctx->h_big.resize(total);
-    ctx->h_space_of.resize(total);
+    std::vector<uint4> old_meta;
+    std::vector<BodyProps> old_props;
+    cudaStream_t st = ctx->stream;
+    if (keep_state) {
+        old_meta.resize(n);
+        old_props.resize(n);
+        for (int i = 0; i < n; i++) {
+            BPC_CHECK(cudaMemcpyAsync(&old_meta[i], ctx->meta.p + slots[i], sizeof(uint4), cudaMemcpyDeviceToHost, st));
+            BPC_CHECK(cudaMemcpyAsync(&old_props[i], ctx->props.p + slots[i], sizeof(BodyProps), cudaMemcpyDeviceToHost, st));
+        }
+        BPC_CHECK(cudaStreamSynchronize(st));
+    }
+    bool any_kin = false;
     for (int i = 0; i < n; i++) {
         const bpc_body_desc &d = descs[i];
         const ShapeRec &sh = ctx->h_shapes[d.shape];
+        uint32_t slot = slots[i];
         xf[i] = pack_xf(d.xf);
         sxf[i] = pack_xf(d.shape_xf);
         memset(&vel[i], 0, sizeof(BodyVel));
@@ -212,16 +256,27 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
         mass_properties(sh, d, props[i], inv_mass);
         memset(&mw[i], 0, sizeof(BodyMassW));
         mw[i].m = make_float4(inv_mass, d.friction, d.bounce, 0.f);
-        uint32_t flags = (d.flags & 1u ? BF_CAN_SLEEP : 0u) | (d.flags & 4u ? 0u : BF_ACTIVE) | (d.flags & 2u ? BF_CCD : 0u);
-        if ((d.flags & 2u) && d.mode >= MODE_RIGID) ctx->h_ccd_ids.push_back(first + i);
+        uint32_t flags = (d.flags & 1u ? BF_CAN_SLEEP : 0u) | (d.flags & 4u ? 0u : BF_ACTIVE) | (d.flags & 2u ? BF_CCD : 0u) |
+                         (d.flags & 16u ? BF_LIN_REPLACE : 0u) | (d.flags & 32u ? BF_ANG_REPLACE : 0u) | (d.flags & 64u ? BF_OMIT_FORCE : 0u) |
+                         (((d.flags >> 8) & 63u) << BF_LOCK_SHIFT);
+        if (keep_state) {
+            uint32_t of = old_meta[i].x >> 8;
+            flags = (flags & ~BF_ACTIVE) | (of & BF_ACTIVE);
+            // set_mode: a body that becomes rigid is woken, one that becomes static or kinematic is not active (bradot_body_3d.cpp:300-340)
+            if ((old_meta[i].x & 0xffu) != d.mode && d.mode >= MODE_RIGID) flags |= BF_ACTIVE;
+            props[i].a2.w = old_props[i].a2.w;
+            props[i].prev_lin = old_props[i].prev_lin;
+            props[i].prev_ang = old_props[i].prev_ang;
+        }
         // a kinematic body is inactive until it is given somewhere to go (set_mode: bradot_body_3d.cpp:218-231), and its
         // velocities are whatever its moves imply
-        if (d.mode == MODE_STATIC || d.mode == MODE_KINEMATIC) flags &= ~BF_ACTIVE;
+        if (d.mode == MODE_STATIC || (d.mode == MODE_KINEMATIC && !(keep_state && (old_meta[i].x & 0xffu) == MODE_KINEMATIC))) flags &= ~BF_ACTIVE;
         if (d.mode == MODE_KINEMATIC) {
             vel[i].lin = make_float4(0.f, 0.f, 0.f, 0.f);
             vel[i].ang = make_float4(0.f, 0.f, 0.f, 0.f);
-            ctx->h_kin_ids.push_back(first + i);
+            any_kin = true;
         }
+        if (!ctx->spaces[d.space].active) flags |= BF_FROZEN;
         bool ident = true;
         for (int q = 0; q < 12; q++) ident = ident && d.shape_xf[q] == ((q == 0 || q == 4 || q == 8) ? 1.f : 0.f);
         if (ident) flags |= BF_SHAPE_IDENT;
@@ -230,75 +285,328 @@ extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, i
         ctx->shape_type_mask |= 1u << sh.meta.x;
         if (sh.meta.x == SH_CONVEX) memcpy(&sp[i].x, &sh.meta.y, 4);
         sid[i] = d.shape;
-        ctx->h_mode[first + i] = (uint8_t)d.mode;
-        ctx->h_space_of[first + i] = d.space;
-        ctx->h_big[first + i] = (d.mode == MODE_STATIC && sh.meta.x == SH_PLANE) ? 1 : 0;
+        ctx->h_mode[slot] = (uint8_t)d.mode;
+        ctx->h_space_of[slot] = d.space;
+        ctx->h_big[slot] = (d.mode == MODE_STATIC && sh.meta.x == SH_PLANE) ? 1 : 0;
+        ctx->h_ccd[slot] = (d.flags & 2u) ? 1 : 0;
+        ctx->h_dead[slot] = 0;
     }
-    cudaStream_t st = ctx->stream;
-    BPC_CHECK(cudaMemcpyAsync(ctx->xf.p + first, xf.data(), n * sizeof(BodyXf), cudaMemcpyHostToDevice, st));
-    BPC_CHECK(cudaMemcpyAsync(ctx->shape_xf.p + first, sxf.data(), n * sizeof(BodyXf), cudaMemcpyHostToDevice, st));
-    BPC_CHECK(cudaMemcpyAsync(ctx->vel.p + first, vel.data(), n * sizeof(BodyVel), cudaMemcpyHostToDevice, st));
-    BPC_CHECK(cudaMemcpyAsync(ctx->massw.p + first, mw.data(), n * sizeof(BodyMassW), cudaMemcpyHostToDevice, st));
-    BPC_CHECK(cudaMemcpyAsync(ctx->props.p + first, props.data(), n * sizeof(BodyProps), cudaMemcpyHostToDevice, st));
-    BPC_CHECK(cudaMemcpyAsync(ctx->meta.p + first, meta.data(), n * sizeof(uint4), cudaMemcpyHostToDevice, st));
-    BPC_CHECK(cudaMemcpyAsync(ctx->shape_id.p + first, sid.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-    BPC_CHECK(cudaMemcpyAsync(ctx->shape_p.p + first, sp.data(), n * sizeof(float4), cudaMemcpyHostToDevice, st));
-    BPC_CHECK(cudaMemsetAsync(ctx->forces.p + first, 0, n * sizeof(BodyForces), st));
-    BPC_CHECK(cudaMemsetAsync(ctx->items.p + first, 0, n * sizeof(ItemBox), st));
-    BPC_CHECK(cudaMemsetAsync(ctx->npairs.p + first, 0, n * sizeof(uint32_t), st));
-    ctx->n_bodies = (uint32_t)total;
-    if (!ctx->h_ccd_ids.empty()) {
-        ctx->ccd_ids.reserve(ctx->h_ccd_ids.size(), false, st);
-        if (!ctx->ccd_ids.p) return fail(ctx, "bpc_bodies_create: out of device memory");
-        BPC_CHECK(cudaMemcpyAsync(ctx->ccd_ids.p, ctx->h_ccd_ids.data(), ctx->h_ccd_ids.size() * 4, cudaMemcpyHostToDevice, st));
+    if (any_kin && !ctx->kin.p) {
+        ctx->kin.reserve(ctx->xf.cap, false, st);
+        if (!ctx->kin.p) return fail(ctx, "out of device memory");
     }
-    if (!ctx->h_kin_ids.empty()) {
-        ctx->kin.reserve(total, true, st);
-        ctx->kin_ids.reserve(ctx->h_kin_ids.size(), false, st);
-        if (!ctx->kin.p || !ctx->kin_ids.p || ctx->kin.cap < total) return fail(ctx, "bpc_bodies_create: out of device memory");
-        BPC_CHECK(cudaMemcpyAsync(ctx->kin_ids.p, ctx->h_kin_ids.data(), ctx->h_kin_ids.size() * 4, cudaMemcpyHostToDevice, st));
+    if (!keep_state) {
+        if (put(ctx, ctx->xf, xf, slots, consecutive) || put(ctx, ctx->vel, vel, slots, consecutive)) return -1;
+    }
+    if (put(ctx, ctx->shape_xf, sxf, slots, consecutive) || put(ctx, ctx->massw, mw, slots, consecutive) || put(ctx, ctx->props, props, slots, consecutive) ||
+        put(ctx, ctx->meta, meta, slots, consecutive) || put(ctx, ctx->shape_id, sid, slots, consecutive) || put(ctx, ctx->shape_p, sp, slots, consecutive))
+        return -1;
+    if (!keep_state) {
         for (int i = 0; i < n; i++) {
-            if (descs[i].mode != MODE_KINEMATIC) continue;
-            KinState k;
-            k.target = xf[i];
-            k.clin = make_float4(descs[i].linvel[0], descs[i].linvel[1], descs[i].linvel[2], 0.f);
-            k.cang = make_float4(descs[i].angvel[0], descs[i].angvel[1], descs[i].angvel[2], 0.f);
-            BPC_CHECK(cudaMemcpyAsync(ctx->kin.p + first + i, &k, sizeof(KinState), cudaMemcpyHostToDevice, st));
-            BPC_CHECK(cudaStreamSynchronize(st)); // k is a stack temporary
+            if (consecutive && i > 0) break;
+            size_t cnt = consecutive ? (size_t)n : 1;
+            BPC_CHECK(cudaMemsetAsync(ctx->forces.p + slots[i], 0, cnt * sizeof(BodyForces), st));
+            BPC_CHECK(cudaMemsetAsync(ctx->items.p + slots[i], 0, cnt * sizeof(ItemBox), st));
+            BPC_CHECK(cudaMemsetAsync(ctx->npairs.p + slots[i], 0, cnt * sizeof(uint32_t), st));
         }
     }
-    // two shape-update passes, as the engine does: creation, then the pending-shape flush at the
-    // start of the first step (P3D/bradot_physics_server_3d.cpp:1728-1733)
-    if (bpc_launch_refresh_bodies(ctx, first, (uint32_t)n, 2)) return -1;
+    std::vector<KinState> ks;
+    for (int i = 0; i < n; i++) {
+        if (descs[i].mode != MODE_KINEMATIC) continue;
+        if (keep_state && (old_meta[i].x & 0xffu) == MODE_KINEMATIC) continue; // target and constant velocities stay
+        if (keep_state) { // becomes kinematic where it is: target = current transform (device-to-device)
+            BPC_CHECK(cudaMemcpyAsync(&ctx->kin.p[slots[i]].target, ctx->xf.p + slots[i], sizeof(BodyXf), cudaMemcpyDeviceToDevice, st));
+            BPC_CHECK(cudaMemsetAsync(&ctx->kin.p[slots[i]].clin, 0, 2 * sizeof(float4), st));
+            continue;
+        }
+        KinState k;
+        k.target = xf[i];
+        k.clin = make_float4(descs[i].linvel[0], descs[i].linvel[1], descs[i].linvel[2], 0.f);
+        k.cang = make_float4(descs[i].angvel[0], descs[i].angvel[1], descs[i].angvel[2], 0.f);
+        ks.push_back(k);
+        BPC_CHECK(cudaMemcpyAsync(ctx->kin.p + slots[i], &ks.back(), sizeof(KinState), cudaMemcpyHostToDevice, st));
+        BPC_CHECK(cudaStreamSynchronize(st)); // ks may reallocate
+    }
+    BPC_CHECK(cudaStreamSynchronize(st)); // the host vectors go out of scope
+    // shape-update passes: creation stores the exact box, then the pending-shape flush at the start of the first step
+    // re-stores it with the growth (P3D/bradot_physics_server_3d.cpp:1728-1733); a re-described body moves its item as
+    // _shapes_changed -> _update_shapes does
+    for (int i = 0; i < n; i++) {
+        if (consecutive && i > 0) break;
+        uint32_t cnt = consecutive ? (uint32_t)n : 1u;
+        if (keep_state) {
+            if (bpc_launch_refresh_bodies(ctx, slots[i], cnt, -2)) return -1;
+        } else if (bpc_launch_refresh_bodies(ctx, slots[i], cnt, 2)) {
+            return -1;
+        }
+    }
     BPC_CHECK(cudaStreamSynchronize(st));
-    if (rebuild_item_lists(ctx)) return -1;
+    ctx->lists_dirty = true;
+    return 0;
+}
+
+static void grow_mirrors(bpc_context *ctx, size_t total) {
+    ctx->h_mode.resize(total);
+    ctx->h_big.resize(total);
+    ctx->h_space_of.resize(total);
+    ctx->h_ccd.resize(total);
+    ctx->h_dead.resize(total);
+}
+
+extern "C" int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, int n) {
+    if (!ctx) return -1;
+    if (n <= 0 || !descs) return fail(ctx, "bpc_bodies_create: no bodies given");
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (validate_descs(ctx, descs, n, "bpc_bodies_create")) return -1;
+    uint32_t first = ctx->n_bodies;
+    size_t total = (size_t)first + n;
+    if (!grow_bodies(ctx, total)) return fail(ctx, "bpc_bodies_create: out of device memory");
+    if (bpc_flush_tables(ctx)) return -1;
+    grow_mirrors(ctx, total);
+    std::vector<uint32_t> slots(n);
+    for (int i = 0; i < n; i++) slots[i] = first + (uint32_t)i;
+    ctx->n_bodies = (uint32_t)total;
+    if (write_body_slots(ctx, slots.data(), descs, n, false)) return -1;
     return (int)first;
 }
 
+extern "C" int bpc_bodies_create_slots(bpc_context *ctx, const bpc_body_desc *descs, int n, int32_t *slots_out) {
+    if (!ctx) return -1;
+    if (n <= 0 || !descs || !slots_out) return fail(ctx, "bpc_bodies_create_slots: no bodies given");
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (validate_descs(ctx, descs, n, "bpc_bodies_create_slots")) return -1;
+    std::vector<uint32_t> slots(n);
+    uint32_t fresh = 0;
+    for (int i = 0; i < n; i++) {
+        if (!ctx->free_slots.empty()) {
+            slots[i] = ctx->free_slots.back();
+            ctx->free_slots.pop_back();
+        } else {
+            slots[i] = ctx->n_bodies + fresh++;
+        }
+    }
+    size_t total = (size_t)ctx->n_bodies + fresh;
+    if (fresh) {
+        if (!grow_bodies(ctx, total)) return fail(ctx, "bpc_bodies_create_slots: out of device memory");
+        grow_mirrors(ctx, total);
+    }
+    if (bpc_flush_tables(ctx)) return -1;
+    ctx->n_bodies = (uint32_t)total;
+    // runs of consecutive slots go down together
+    int i = 0;
+    while (i < n) {
+        int j = i + 1;
+        while (j < n && slots[j] == slots[j - 1] + 1) j++;
+        if (write_body_slots(ctx, slots.data() + i, descs + i, j - i, false)) return -1;
+        i = j;
+    }
+    for (int k = 0; k < n; k++) slots_out[k] = (int32_t)slots[k];
+    return 0;
+}
+
+extern "C" int bpc_bodies_update(bpc_context *ctx, const int32_t *slots, int n, const bpc_body_desc *descs, int keep_state) {
+    if (!ctx) return -1;
+    if (n <= 0 || !descs || !slots) return fail(ctx, "bpc_bodies_update: no bodies given");
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (validate_descs(ctx, descs, n, "bpc_bodies_update")) return -1;
+    for (int i = 0; i < n; i++) {
+        if (slots[i] < 0 || (uint32_t)slots[i] >= ctx->n_bodies || ctx->h_dead[slots[i]]) return fail(ctx, "bpc_bodies_update: invalid body");
+    }
+    if (bpc_flush_tables(ctx)) return -1;
+    if (bpc_resolve_step(ctx)) return -1;
+    for (int i = 0; i < n; i++) {
+        uint32_t s = (uint32_t)slots[i];
+        if (write_body_slots(ctx, &s, descs + i, 1, keep_state != 0)) return -1;
+    }
+    return 0;
+}
+
+// tombstone of a destroyed body: static, frozen, no layers (nothing interacts with it), outside every list
+__global__ void k_bury_bodies(uint32_t n, const uint32_t *__restrict__ slots, uint4 *__restrict__ meta, BodyVel *__restrict__ vel,
+                              BodyForces *__restrict__ forces, uint32_t *__restrict__ npairs) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    uint32_t i = slots[t];
+    meta[i] = make_uint4(MODE_STATIC | ((BF_FROZEN | BF_SHAPE_IDENT) << 8) | (meta[i].x & 0xff000000u), 0u, 0u, meta[i].w);
+    BodyVel z;
+    z.lin = z.ang = z.blin = z.bang = make_float4(0.f, 0.f, 0.f, 0.f);
+    vel[i] = z;
+    BodyForces f;
+    f.force = f.torque = f.cforce = f.ctorque = make_float4(0.f, 0.f, 0.f, 0.f);
+    forces[i] = f;
+    npairs[i] = 0;
+}
+// wakeup_neighbours (bradot_body_3d.cpp:740-760): rigid bodies sharing a pair with a marked body are activated
+__global__ void k_wake_neighbours(uint32_t n_pairs, const uint64_t *__restrict__ keys, const uint32_t *__restrict__ mark, uint4 *__restrict__ meta) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_pairs) return;
+    uint64_t key = keys[k];
+    uint32_t a = (uint32_t)(key >> 32), b = (uint32_t)key;
+    bool ma = mark[a >> 5] & (1u << (a & 31)), mb = mark[b >> 5] & (1u << (b & 31));
+    if (!ma && !mb) return;
+    uint32_t other = ma ? b : a;
+    for (int side = 0; side < 2; side++) {
+        if (side == 1) {
+            if (!(ma && mb)) break;
+            other = a;
+        }
+        uint32_t m = meta[other].x;
+        if ((m & 0xffu) >= MODE_RIGID && !((m >> 8) & (BF_ACTIVE | BF_FROZEN))) atomicOr(&meta[other].x, BF_ACTIVE << 8);
+    }
+}
+
+// wake the rigid bodies that share a broadphase pair with one of `who` (host list of body indices)
+int bpc_wake_neighbours(bpc_context *ctx, const std::vector<uint32_t> &who) {
+    uint32_t np = ctx->n_pairs[ctx->cur];
+    if (who.empty() || !np) return 0;
+    size_t words = (ctx->n_bodies + 31) / 32;
+    std::vector<uint32_t> mark(words, 0);
+    for (uint32_t i : who) mark[i >> 5] |= 1u << (i & 31);
+    cudaStream_t st = ctx->stream;
+    ctx->vals_alt.reserve(words, false, st);
+    if (!ctx->vals_alt.p) return fail(ctx, "out of device memory");
+    BPC_CHECK(cudaMemcpyAsync(ctx->vals_alt.p, mark.data(), words * 4, cudaMemcpyHostToDevice, st));
+    k_wake_neighbours<<<(np + 255) / 256, 256, 0, st>>>(np, ctx->pair_keys[ctx->cur].p, ctx->vals_alt.p, ctx->meta.p);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int bpc_joints_destroy_of_bodies(bpc_context *ctx, const std::vector<uint8_t> &gone);
+
+extern "C" int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n) {
+    if (!ctx) return -1;
+    if (n <= 0 || !slots) return fail(ctx, "bpc_bodies_destroy: no bodies given");
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    std::vector<uint32_t> s;
+    for (int i = 0; i < n; i++) {
+        if (slots[i] < 0 || (uint32_t)slots[i] >= ctx->n_bodies) return fail(ctx, "bpc_bodies_destroy: invalid body");
+        if (!ctx->h_dead[slots[i]]) s.push_back((uint32_t)slots[i]);
+    }
+    if (s.empty()) return 0;
+    if (bpc_resolve_step(ctx)) return -1;
+    cudaStream_t st = ctx->stream;
+    // No body is woken: the reference unpairs the body first (set_space(nullptr)), so by the time its shapes go and
+    // _shapes_changed() calls wakeup_neighbours() its constraint map is empty -- a sleeping box on top of a freed one sleeps on.
+    ctx->vals.reserve(s.size(), false, st);
+    if (!ctx->vals.p) return fail(ctx, "out of device memory");
+    BPC_CHECK(cudaMemcpyAsync(ctx->vals.p, s.data(), s.size() * 4, cudaMemcpyHostToDevice, st));
+    k_bury_bodies<<<((uint32_t)s.size() + 127) / 128, 128, 0, st>>>((uint32_t)s.size(), ctx->vals.p, ctx->meta.p, ctx->vel.p, ctx->forces.p, ctx->npairs.p);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaStreamSynchronize(st));
+    std::vector<uint8_t> gone(ctx->n_bodies, 0);
+    for (uint32_t i : s) {
+        ctx->h_dead[i] = 1;
+        ctx->h_mode[i] = MODE_STATIC;
+        ctx->h_big[i] = 0;
+        ctx->h_ccd[i] = 0;
+        ctx->free_slots.push_back(i);
+        gone[i] = 1;
+    }
+    // collision exceptions that name a destroyed body go with it
+    size_t before = ctx->h_except.size();
+    ctx->h_except.erase(std::remove_if(ctx->h_except.begin(), ctx->h_except.end(),
+                                       [&](uint64_t k) { return gone[(uint32_t)(k >> 32)] || gone[(uint32_t)k]; }),
+                        ctx->h_except.end());
+    if (ctx->h_except.size() != before) ctx->except_dirty = true;
+    if (bpc_joints_destroy_of_bodies(ctx, gone)) return -1;
+    ctx->lists_dirty = true;
+    return 0;
+}
+
 extern "C" int bpc_body_count(bpc_context *ctx) { return ctx ? (int)ctx->n_bodies : -1; }
+
+// ---------------------------------------------------------------------------------------------- joints
+static void joint_defaults(JointRec &j) {
+    if (j.flags & JF_HAS_PARAMS) return;
+    memset(j.prm, 0, sizeof(j.prm));
+    if (j.type == BPC_JOINT_PIN) { // bradot_pin_joint_3d.h: m_tau 0.3, m_damping 1, m_impulseClamp 0
+        j.prm[0] = 0.3f; j.prm[1] = 1.0f; j.prm[2] = 0.0f;
+    } else { // bradot_hinge_joint_3d.h:73-88: tau 0.3, upper -pi, lower pi, bias 0.3, softness 0.9, relaxation 1, motor 0 / 0
+        j.prm[0] = 0.3f; j.prm[1] = (float)-3.14159265358979323846; j.prm[2] = (float)3.14159265358979323846;
+        j.prm[3] = 0.3f; j.prm[4] = 0.9f; j.prm[5] = 1.0f; j.prm[6] = 0.0f; j.prm[7] = 0.0f;
+    }
+}
+
+// collision exceptions are those of the live joints that ask for them
+static void rebuild_exceptions(bpc_context *ctx) {
+    ctx->h_except.clear();
+    ctx->max_priority = 1;
+    for (const JointRec &j : ctx->h_joints) {
+        if (j.flags & JF_DEAD) continue;
+        if (j.flags & 1u) ctx->h_except.push_back(((uint64_t)std::min(j.a, j.b) << 32) | std::max(j.a, j.b));
+        ctx->max_priority = std::max(ctx->max_priority, j.priority);
+    }
+    ctx->except_dirty = true;
+}
+
+static int joint_from_desc(bpc_context *ctx, const bpc_joint_desc &d, JointRec &j) {
+    static_assert(sizeof(JointRec) == sizeof(bpc_joint_desc), "JointRec mirrors bpc_joint_desc");
+    if (d.body_a >= ctx->n_bodies || d.body_b >= ctx->n_bodies || d.body_a == d.body_b || ctx->h_dead[d.body_a] || ctx->h_dead[d.body_b])
+        return fail(ctx, "joint: invalid body");
+    if (d.type > BPC_JOINT_HINGE) return fail(ctx, "joint: unsupported joint type (pin, hinge)");
+    if (d.priority > 15) return fail(ctx, "joint: solver priority above 15");
+    memcpy(&j, &d, sizeof(JointRec));
+    j.flags &= ~JF_DEAD;
+    if (j.priority == 0) j.priority = 1;
+    joint_defaults(j);
+    return 0;
+}
 
 extern "C" int bpc_joints_create(bpc_context *ctx, const bpc_joint_desc *descs, int n) {
     if (!ctx) return -1;
     if (n <= 0 || !descs) return fail(ctx, "bpc_joints_create: no joints given");
     int first = (int)ctx->h_joints.size();
+    std::vector<JointRec> recs(n);
     for (int i = 0; i < n; i++) {
-        const bpc_joint_desc &d = descs[i];
-        if (d.body_a >= ctx->n_bodies || d.body_b >= ctx->n_bodies || d.body_a == d.body_b) return fail(ctx, "bpc_joints_create: invalid body");
-        if (d.type > BPC_JOINT_HINGE) return fail(ctx, "bpc_joints_create: unsupported joint type (pin, hinge)");
-        JointRec j;
-        j.type = d.type; j.a = d.body_a; j.b = d.body_b; j.flags = d.flags;
-        memcpy(j.fa, d.frame_a, sizeof(j.fa));
-        memcpy(j.fb, d.frame_b, sizeof(j.fb));
-        ctx->h_joints.push_back(j);
-        if (d.flags & 1u) {
-            uint32_t a = std::min(d.body_a, d.body_b), b = std::max(d.body_a, d.body_b);
-            ctx->h_except.push_back(((uint64_t)a << 32) | b);
-            ctx->except_dirty = true;
-        }
+        if (joint_from_desc(ctx, descs[i], recs[i])) return -1;
     }
+    ctx->h_joints.insert(ctx->h_joints.end(), recs.begin(), recs.end());
+    rebuild_exceptions(ctx);
     ctx->joints_dirty = true;
     return first;
 }
+
+extern "C" int bpc_joints_write(bpc_context *ctx, int first, int n, const bpc_joint_desc *descs) {
+    if (!ctx) return -1;
+    if (first < 0 || n < 0 || (size_t)first + n > ctx->h_joints.size() || (n > 0 && !descs)) return fail(ctx, "bpc_joints_write: range out of bounds");
+    for (int i = 0; i < n; i++) {
+        JointRec &old = ctx->h_joints[first + i], j;
+        if (old.flags & JF_DEAD) return fail(ctx, "bpc_joints_write: joint was destroyed");
+        if (joint_from_desc(ctx, descs[i], j)) return -1;
+        if (j.type != old.type || j.a != old.a || j.b != old.b) return fail(ctx, "bpc_joints_write: type and bodies of a joint cannot change");
+        old = j;
+    }
+    rebuild_exceptions(ctx);
+    ctx->joints_dirty = true;
+    return 0;
+}
+
+extern "C" int bpc_joints_destroy(bpc_context *ctx, int first, int n) {
+    if (!ctx) return -1;
+    if (first < 0 || n < 0 || (size_t)first + n > ctx->h_joints.size()) return fail(ctx, "bpc_joints_destroy: range out of bounds");
+    for (int i = 0; i < n; i++) ctx->h_joints[first + i].flags |= JF_DEAD;
+    rebuild_exceptions(ctx);
+    ctx->joints_dirty = true;
+    return 0;
+}
+
+int bpc_joints_destroy_of_bodies(bpc_context *ctx, const std::vector<uint8_t> &gone) {
+    bool any = false;
+    for (JointRec &j : ctx->h_joints) {
+        if (!(j.flags & JF_DEAD) && (gone[j.a] || gone[j.b])) {
+            j.flags |= JF_DEAD;
+            any = true;
+        }
+    }
+    if (any) {
+        rebuild_exceptions(ctx);
+        ctx->joints_dirty = true;
+    }
+    return 0;
+}
+
+extern "C" int bpc_joint_count(bpc_context *ctx) { return ctx ? (int)ctx->h_joints.size() : -1; }
 
 // ---------------------------------------------------------------------------------------------- bulk state I/O
 // The per-tick paths of an engine (read every transform / velocity, write the force accumulators) repack on the
@@ -541,5 +849,139 @@ extern "C" int bpc_bodies_write(bpc_context *ctx, int field, int first, int n, c
         if (bpc_launch_refresh_bodies(ctx, (uint32_t)first, (uint32_t)n, -1)) return -1;
         BPC_CHECK(cudaStreamSynchronize(ctx->stream));
     }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- body_set_state semantics
+// One thread per listed body.  BradotBody3D::set_state (bradot_body_3d.cpp:352-417) with its side effects:
+// orthonormalised rigid transforms, world mass data and broadphase item following the transform, wake-ups.
+int bpc_wake_neighbours(bpc_context *ctx, const std::vector<uint32_t> &who);
+
+static int stage_slots(bpc_context *ctx, const int32_t *slots, int n, const char *who) {
+    for (int i = 0; i < n; i++) {
+        if (slots[i] < 0 || (uint32_t)slots[i] >= ctx->n_bodies) return fail(ctx, (std::string(who) + ": invalid body").c_str());
+    }
+    ctx->io_slots.reserve((size_t)n, false, ctx->stream);
+    if (!ctx->io_slots.p) return fail(ctx, "out of device memory");
+    BPC_CHECK(cudaMemcpyAsync(ctx->io_slots.p, slots, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    return 0;
+}
+
+extern "C" int bpc_bodies_set_state(bpc_context *ctx, int state, const int32_t *slots, int n, const float *values) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && (!slots || !values))) return fail(ctx, "bpc_bodies_set_state: bad arguments");
+    int width = state == BPC_STATE_TRANSFORM ? 12 : (state == BPC_STATE_LINEAR_VELOCITY || state == BPC_STATE_ANGULAR_VELOCITY) ? 3 :
+                (state == BPC_STATE_SLEEPING || state == BPC_STATE_CAN_SLEEP) ? 1 : 0;
+    if (!width) return fail(ctx, "bpc_bodies_set_state: unknown state");
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (bpc_flush_tables(ctx) || bpc_resolve_step(ctx)) return -1;
+    if (stage_slots(ctx, slots, n, "bpc_bodies_set_state") || staging_for(ctx, (size_t)n * width)) return -1;
+    cudaStream_t st = ctx->stream;
+    BPC_CHECK(cudaMemcpyAsync(ctx->staging.p, values, (size_t)n * width * sizeof(float), cudaMemcpyHostToDevice, st));
+    bool statics = false;
+    if (state == BPC_STATE_TRANSFORM) {
+        for (int i = 0; i < n && !statics; i++) statics = ctx->h_mode[slots[i]] == MODE_STATIC;
+    }
+    size_t words = (ctx->n_bodies + 31) / 32;
+    if (statics) {
+        ctx->vals_alt.reserve(words, false, st);
+        if (!ctx->vals_alt.p) return fail(ctx, "out of device memory");
+        BPC_CHECK(cudaMemsetAsync(ctx->vals_alt.p, 0, words * 4, st));
+    }
+    SetStateArgs a;
+    a.n = (uint32_t)n;
+    a.state = state;
+    a.slots = ctx->io_slots.p;
+    a.values = ctx->staging.p;
+    a.xf = ctx->xf.p; a.vel = ctx->vel.p; a.massw = ctx->massw.p; a.props = ctx->props.p; a.meta = ctx->meta.p; a.kin = ctx->kin.p;
+    a.shape_xf = ctx->shape_xf.p; a.shape_id = ctx->shape_id.p; a.shapes = ctx->shapes.p; a.items = ctx->items.p; a.npairs = ctx->npairs.p;
+    a.moved_static = ctx->vals_alt.p;
+    if (bpc_launch_set_state(ctx, a)) return -1;
+    if (statics) {
+        uint32_t np = ctx->n_pairs[ctx->cur];
+        if (np) k_wake_neighbours<<<(np + 255) / 256, 256, 0, st>>>(np, ctx->pair_keys[ctx->cur].p, ctx->vals_alt.p, ctx->meta.p);
+        BPC_CHECK(cudaGetLastError());
+    }
+    BPC_CHECK(cudaStreamSynchronize(st)); // the caller may reuse its buffers
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- gather / scatter I/O
+__global__ void k_gather_rows(uint32_t n, const uint32_t *__restrict__ slots, int field, const BodyXf *__restrict__ xf, const BodyVel *__restrict__ vel,
+                              const uint4 *__restrict__ meta, float *__restrict__ out) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    uint32_t i = slots ? slots[t] : t;
+    if (field == BPC_FIELD_TRANSFORM || field < 0) {
+        BodyXf x = xf[i];
+        float *o = out + (size_t)t * (field < 0 ? 19 : 12);
+        o[0] = x.r0.x; o[1] = x.r0.y; o[2] = x.r0.z; o[3] = x.r1.x; o[4] = x.r1.y; o[5] = x.r1.z;
+        o[6] = x.r2.x; o[7] = x.r2.y; o[8] = x.r2.z; o[9] = x.o.x; o[10] = x.o.y; o[11] = x.o.z;
+        if (field < 0) {
+            BodyVel v = vel[i];
+            o[12] = v.lin.x; o[13] = v.lin.y; o[14] = v.lin.z; o[15] = v.ang.x; o[16] = v.ang.y; o[17] = v.ang.z;
+            o[18] = ((meta[i].x >> 8) & BF_ACTIVE) ? 1.f : 0.f;
+        }
+    } else if (field == BPC_FIELD_LINEAR_VELOCITY || field == BPC_FIELD_ANGULAR_VELOCITY) {
+        float4 v = field == BPC_FIELD_ANGULAR_VELOCITY ? vel[i].ang : vel[i].lin;
+        out[(size_t)t * 3] = v.x; out[(size_t)t * 3 + 1] = v.y; out[(size_t)t * 3 + 2] = v.z;
+    } else if (field == BPC_FIELD_ACTIVE) {
+        out[t] = ((meta[i].x >> 8) & BF_ACTIVE) ? 1.f : 0.f;
+    }
+}
+__global__ void k_scatter_forces(uint32_t n, const uint32_t *__restrict__ slots, const float *__restrict__ in, BodyForces *__restrict__ forces,
+                                 uint4 *__restrict__ meta) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    uint32_t i = slots[t];
+    const float *o = in + (size_t)t * 6;
+    forces[i].force = make_float4(o[0], o[1], o[2], 0.f);
+    forces[i].torque = make_float4(o[3], o[4], o[5], 0.f);
+    if (o[0] != 0.f || o[1] != 0.f || o[2] != 0.f || o[3] != 0.f || o[4] != 0.f || o[5] != 0.f) {
+        uint32_t m = meta[i].x;
+        if ((m & 0xffu) >= MODE_RIGID && !((m >> 8) & (BF_ACTIVE | BF_FROZEN))) meta[i].x = m | (BF_ACTIVE << 8);
+    }
+}
+
+extern "C" int bpc_bodies_read_slots(bpc_context *ctx, int field, const int32_t *slots, int n, float *out) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && (!slots || !out))) return fail(ctx, "bpc_bodies_read_slots: bad arguments");
+    int width = field == BPC_FIELD_TRANSFORM ? 12 : (field == BPC_FIELD_LINEAR_VELOCITY || field == BPC_FIELD_ANGULAR_VELOCITY) ? 3 : field == BPC_FIELD_ACTIVE ? 1 : 0;
+    if (!width) return fail(ctx, "bpc_bodies_read_slots: field must be TRANSFORM, LINEAR_VELOCITY, ANGULAR_VELOCITY or ACTIVE");
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (bpc_resolve_step(ctx)) return -1;
+    if (stage_slots(ctx, slots, n, "bpc_bodies_read_slots") || staging_for(ctx, (size_t)n * width)) return -1;
+    k_gather_rows<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->io_slots.p, field, ctx->xf.p, ctx->vel.p, ctx->meta.p, ctx->staging.p);
+    BPC_CHECK(cudaMemcpyAsync(out, ctx->staging.p, (size_t)n * width * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    BPC_CHECK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int bpc_bodies_write_slots(bpc_context *ctx, int field, const int32_t *slots, int n, const float *in) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && (!slots || !in))) return fail(ctx, "bpc_bodies_write_slots: bad arguments");
+    if (field != BPC_FIELD_APPLIED_FORCE) return fail(ctx, "bpc_bodies_write_slots: field must be APPLIED_FORCE (state goes through bpc_bodies_set_state)");
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (bpc_resolve_step(ctx)) return -1;
+    if (stage_slots(ctx, slots, n, "bpc_bodies_write_slots") || staging_for(ctx, (size_t)n * 6)) return -1;
+    BPC_CHECK(cudaMemcpyAsync(ctx->staging.p, in, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    k_scatter_forces<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->io_slots.p, ctx->staging.p, ctx->forces.p, ctx->meta.p);
+    BPC_CHECK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int bpc_bodies_read_state(bpc_context *ctx, int first, int n, float *out) {
+    if (!ctx) return -1;
+    if (first < 0 || n < 0 || (uint32_t)(first + n) > ctx->n_bodies || (n > 0 && !out)) return fail(ctx, "bpc_bodies_read_state: range out of bounds");
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (bpc_resolve_step(ctx)) return -1;
+    if (staging_for(ctx, (size_t)n * 19)) return -1;
+    k_gather_rows<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, nullptr, -1, ctx->xf.p + first, ctx->vel.p + first, ctx->meta.p + first, ctx->staging.p);
+    BPC_CHECK(cudaMemcpyAsync(out, ctx->staging.p, (size_t)n * 19 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    BPC_CHECK(cudaStreamSynchronize(ctx->stream));
     return 0;
 }

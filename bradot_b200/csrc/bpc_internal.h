@@ -19,6 +19,9 @@ enum { MODE_STATIC = 0, MODE_KINEMATIC = 1, MODE_RIGID = 2, MODE_RIGID_LINEAR = 
 #define BF_CCD 2u
 #define BF_ACTIVE 4u
 #define BF_OMIT_FORCE 8u
+#define BF_FROZEN 16u      // the body's space is inactive (space_set_active(false)) or the body was destroyed: no stage touches it
+#define BF_LIN_REPLACE 32u // BODY_DAMP_MODE_REPLACE for the linear / angular damping (bradot_body_3d.cpp:586-606)
+#define BF_ANG_REPLACE 64u
 #define BF_LOCK_SHIFT 8 // 6 axis-lock bits, same order as PhysicsServer3D::BodyAxis
 #define BF_SHAPE_IDENT (1u << 14)  // the shape's local transform is the identity (no product needed)
 #define BF_ISLAND_AWAKE (1u << 15) // refreshed every step: the body's island holds an awake body
@@ -97,15 +100,25 @@ struct SpaceParams {
     float sleep_lin = 0.1f, sleep_ang = 0.13962634f, time_to_sleep = 0.5f; // servers/physics_server_3d.cpp:1135-1137
     float recycle_radius = 0.01f, max_separation = 0.05f, max_penetration = 0.01f; // :1139-1141
     int iterations = 16;
+    int active = 1; // space_set_active
+    int alive = 1;  // 0 after bpc_space_destroy
 };
 
 // stages timed by bpc_set_profiling: forces, broadphase, islands, narrowphase, schedule, solve, integrate+sleep
 #define BPC_N_STAGES 7
 
+// Same layout as bpc_joint_desc.  flags: bit0 bodies do not collide, bit1 hinge use_limit, bit2 hinge enable_motor,
+// bit3 prm[] given (else defaults), bit31 destroyed.  prm: pin = bias, damping, impulse clamp; hinge = HingeJointParam order.
 struct JointRec {
     uint32_t type, a, b, flags;
     float fa[12], fb[12];
+    float prm[8];
+    uint32_t priority, pad[3];
 };
+#define JF_USE_LIMIT 2u
+#define JF_ENABLE_MOTOR 4u
+#define JF_HAS_PARAMS 8u
+#define JF_DEAD 0x80000000u
 
 // Per-step joint data written by k_joint_setup (the Jacobian diagonals of BradotJacobianEntry3D and
 // everything about the pivots / axes that stays constant while the solver sweeps).
@@ -114,8 +127,10 @@ struct __align__(16) JointSetup {
     float4 pa;         // pivot A in world minus origin A ; w = flags (bit0 dynamic_A, bit1 dynamic_B, bit2 awake)
     float4 pb;         // pivot B in world minus origin B
     float4 dpos;       // pivotAInW - pivotBInW
-    float4 axis_a;     // hinge axis of A in world
-    float4 axis_b;     // hinge axis of B in world
+    float4 axis_a;     // hinge axis of A in world ; w = kHinge
+    float4 axis_b;     // hinge axis of B in world ; w = limit sign (0 = limit not violated)
+    float4 lim;        // hinge: limit correction, accumulated limit impulse (cleared by the setup), motor target velocity, motor max impulse
+    float4 prm;        // pin: bias, damping, impulse clamp ; hinge: bias, relaxation, limit bias
 };
 
 struct Stats {
@@ -154,6 +169,7 @@ struct bpc_context {
     DevBuf<JointSetup> jsetup;
     DevBuf<uint32_t> a_range_cur; // same for the current pair list (vertex-centric island pass)
     DevBuf<uint32_t> a_range; // [2 * n_bodies]: begin / end of each body's run (as A) in the previous pair list
+    DevBuf<uint32_t> io_slots; // body indices of a gather / scatter call
     DevBuf<float> staging;    // packed per-body floats on their way to / from the host (bulk state I/O)
     DevBuf<uint32_t> np_work; // broadphase pairs that need the full narrowphase pass this step
     DevBuf<uint32_t> np_cwork; // hull-against-hull pairs handed to the warp-per-pair kernel
@@ -222,6 +238,11 @@ struct bpc_context {
     uint32_t shape_type_mask = 0; // shape types present among the bodies (bit = ShapeType)
     std::vector<uint8_t> h_big;  // 1 = unbounded static item (world boundary), kept out of the LBVH
     std::vector<uint8_t> h_mode; // host mirror of the body modes (scheduling of teacher-forced sweeps)
+    std::vector<uint8_t> h_ccd;  // host mirror: continuous collision detection asked for
+    std::vector<uint8_t> h_dead; // 1 = slot of a destroyed body (reused by bpc_bodies_create_slots)
+    std::vector<uint32_t> free_slots;
+    bool lists_dirty = false;    // tree / unbounded-static lists have to be rebuilt before the next step or query
+    uint32_t max_priority = 1;   // highest joint solver priority
 
     // constraints / solver
     DevBuf<uint32_t> con_list, con_color, con_sorted, con_sorted_alt;
@@ -254,19 +275,26 @@ enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIV
         }                                                                                             \
     } while (0)
 
+// Grows to at least n elements.  On failure (out of memory, or a failed copy of the old contents) the buffer is left EMPTY
+// (p == nullptr, cap == 0), so that the `!buf.p` test every caller makes also catches a failed growth -- never the old,
+// smaller allocation that the following kernels would overrun.
 template <typename T>
 void DevBuf<T>::reserve(size_t n, bool keep, cudaStream_t st) {
     if (n <= cap) return;
     size_t ncap = n + n / 4 + 256;
     T *np = nullptr;
-    if (cudaMalloc(&np, ncap * sizeof(T)) != cudaSuccess) {
-        return;
-    }
-    cudaMemsetAsync(np, 0, ncap * sizeof(T), st);
-    if (keep && p && cap) cudaMemcpyAsync(np, p, cap * sizeof(T), cudaMemcpyDeviceToDevice, st);
+    bool ok = cudaMalloc(&np, ncap * sizeof(T)) == cudaSuccess;
+    if (ok) ok = cudaMemsetAsync(np, 0, ncap * sizeof(T), st) == cudaSuccess;
+    if (ok && keep && p && cap) ok = cudaMemcpyAsync(np, p, cap * sizeof(T), cudaMemcpyDeviceToDevice, st) == cudaSuccess;
     if (p) {
         cudaStreamSynchronize(st);
         cudaFree(p);
+    }
+    if (!ok) {
+        cudaGetLastError(); // cudaErrorMemoryAllocation is not sticky: clear it so that it is not blamed on a later call
+        if (np) cudaFree(np);
+        np = nullptr;
+        ncap = 0;
     }
     p = np;
     cap = ncap;
@@ -278,10 +306,35 @@ void DevBuf<T>::free_() {
     cap = 0;
 }
 
+// bpc_bodies_set_state: one thread per listed body (kernel in k_integrate.cu, next to the item / mass-data helpers it uses)
+struct SetStateArgs {
+    uint32_t n;
+    int state;
+    const uint32_t *slots;
+    const float *values; // n rows
+    BodyXf *xf;
+    BodyVel *vel;
+    BodyMassW *massw;
+    BodyProps *props;
+    uint4 *meta;
+    KinState *kin;
+    const BodyXf *shape_xf;
+    const uint32_t *shape_id;
+    const ShapeRec *shapes;
+    ItemBox *items;
+    const uint32_t *npairs;
+    uint32_t *moved_static; // bit per body: a static body was moved (its neighbours are woken afterwards)
+};
+int bpc_launch_set_state(bpc_context *ctx, const SetStateArgs &a);
+
 // ---- kernel launchers (one per .cu file) ------------------------------------------------------
 int bpc_launch_integrate_forces(bpc_context *ctx, float dt);
 int bpc_launch_integrate_velocities(bpc_context *ctx, float dt);
+// passes > 0: creation (pass 0 stores the exact box, later ones re-store it as moves); -1: world mass data only;
+// -2: world mass data + the broadphase item moved as _update_shapes does (hysteresis with the item's pair count)
 int bpc_launch_refresh_bodies(bpc_context *ctx, uint32_t first, uint32_t n, int passes);
+int bpc_rebuild_lists(bpc_context *ctx);
+int bpc_resolve_step(bpc_context *ctx);
 int bpc_launch_broadphase(bpc_context *ctx);
 int bpc_build_tree(bpc_context *ctx); // LBVH over the current stored boxes (also used by the space queries)
 int bpc_launch_islands(bpc_context *ctx);

@@ -122,6 +122,12 @@ extern "C" int bpc_get_stage_times(bpc_context *ctx, double *ms_out, int *steps_
     return 0;
 }
 
+// Everything a finished step leaves for the host to settle before state is read or changed; nothing yet is deferred.
+int bpc_resolve_step(bpc_context *ctx) {
+    (void)ctx;
+    return 0;
+}
+
 extern "C" int bpc_step(bpc_context *ctx, float dt) {
     if (!ctx) return -1;
     if (!(dt > 0.f)) return fail(ctx, "bpc_step: dt must be positive");

@@ -365,6 +365,8 @@ int bpc_ensure_pair_cap(bpc_context *ctx, size_t need) {
 }
 
 int bpc_build_tree(bpc_context *ctx) {
+    // the item lists follow creations, destructions and mode changes; the per-space offsets exist even without bodies
+    if ((ctx->lists_dirty || !ctx->big_start.p || !ctx->big_items.p) && bpc_rebuild_lists(ctx)) return -1;
     uint32_t n = ctx->n_tree;
     if (n == 0) return 0;
     cudaStream_t st = ctx->stream;

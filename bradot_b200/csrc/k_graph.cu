@@ -83,6 +83,7 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_union_joints(uint32_t n, cons
                                                                uint32_t *__restrict__ label) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
+    if (joints[j].flags & JF_DEAD) return;
     uint32_t a = joints[j].a, b = joints[j].b;
     if ((meta[a].x & 0xffu) == MODE_STATIC || (meta[b].x & 0xffu) == MODE_STATIC) return;
     cc_union(label, a, b);
@@ -103,7 +104,8 @@ __global__ void __launch_bounds__(GR_THREADS) k_cc_flatten(uint32_t n, uint32_t 
     label[i] = r;
     uint32_t m = meta[i].x;
     // island holds an awake body; test first: a pile is ONE island and a million atomics on its flag would serialise
-    if ((m & 0xffu) != MODE_STATIC && ((m >> 8) & BF_ACTIVE) && !(((volatile uint32_t *)flag)[r] & 1u)) atomicOr(&flag[r], 1u);
+    // (bodies of an inactive space keep their active flag but wake nothing: BF_FROZEN)
+    if ((m & 0xffu) != MODE_STATIC && ((m >> 8) & (BF_ACTIVE | BF_FROZEN)) == BF_ACTIVE && !(((volatile uint32_t *)flag)[r] & 1u)) atomicOr(&flag[r], 1u);
 }
 
 // per-body copy of "my island is awake" so that pair kernels need no label/flag gathers
@@ -121,7 +123,7 @@ __global__ void __launch_bounds__(GR_THREADS) k_island_bits(uint32_t n, const ui
 __global__ void __launch_bounds__(GR_THREADS) k_island_joint_mark(uint32_t n, const JointRec *__restrict__ joints, const uint4 *__restrict__ meta,
                                                                   const uint32_t *__restrict__ label, uint32_t *__restrict__ flag) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+    if (j >= n || (joints[j].flags & JF_DEAD)) return;
     uint32_t a = joints[j].a, b = joints[j].b;
     uint32_t r = label[(meta[a].x & 0xffu) != MODE_STATIC ? a : b];
     if (!(flag[r] & 8u)) atomicOr(&flag[r], 8u);
@@ -201,8 +203,9 @@ __device__ __forceinline__ void con_bodies(uint32_t id, uint32_t n_pairs, const 
         b = (bits & 0x400u) ? (uint32_t)key : 0xffffffffu;
     } else {
         const JointRec &j = joints[id - n_pairs];
-        a = (meta[j.a].x & 0xffu) > MODE_KINEMATIC ? j.a : 0xffffffffu;
-        b = (meta[j.b].x & 0xffu) > MODE_KINEMATIC ? j.b : 0xffffffffu;
+        bool dead = j.flags & JF_DEAD;
+        a = (!dead && (meta[j.a].x & 0xffu) > MODE_KINEMATIC) ? j.a : 0xffffffffu;
+        b = (!dead && (meta[j.b].x & 0xffu) > MODE_KINEMATIC) ? j.b : 0xffffffffu;
     }
 }
 

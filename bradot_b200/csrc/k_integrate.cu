@@ -9,6 +9,7 @@
 //   bradot_collision_object_3d.cpp:156-184  _update_shapes (AABB with 5 % feedback growth)
 //   core/math/bvh_public.inc:101-188, 473-499 ; core/math/bvh_pair.inc:66-71  item_move hysteresis
 //   bradot_body_3d.cpp:783-800 ; bradot_step_3d.cpp:162-184  sleep_test / _check_suspend
+#include "../../include/bradot_physics_cuda.h"
 #include "bpc_internal.h"
 
 #define IT_THREADS 128
@@ -24,7 +25,7 @@ __global__ void __launch_bounds__(IT_THREADS) k_integrate_forces(uint32_t n, flo
     if (i < n) {
         uint4 mt = meta[i];
         uint32_t mode = mt.x & 0xffu, flags = mt.x >> 8;
-        act = mode != MODE_STATIC && (flags & BF_ACTIVE);
+        act = mode != MODE_STATIC && (flags & BF_ACTIVE) && !(flags & BF_FROZEN);
         if (act) {
             BodyVel v = vel[i];
             BodyProps p = props[i];
@@ -35,8 +36,9 @@ __global__ void __launch_bounds__(IT_THREADS) k_integrate_forces(uint32_t n, flo
                 BodyForces f = forces[i];
                 BodyMassW mw = massw[i];
                 V3 gravity = V3(sp.gravity[0], sp.gravity[1], sp.gravity[2]) * p.iinv_gs.w;
-                float ld = sp.lin_damp + p.a0.w; // BODY_DAMP_MODE_COMBINE
-                float ad = sp.ang_damp + p.a1.w;
+                // the body's own damping is added to the default area's (COMBINE) or takes its place (REPLACE), bradot_body_3d.cpp:586-606
+                float ld = (flags & BF_LIN_REPLACE) ? p.a0.w : sp.lin_damp + p.a0.w;
+                float ad = (flags & BF_ANG_REPLACE) ? p.a1.w : sp.ang_damp + p.a1.w;
                 V3 force = gravity * p.com_mass.w + f4v(f.force) + f4v(f.cforce);
                 V3 torque = f4v(f.torque) + f4v(f.ctorque);
                 float damp = 1.0f - dt * ld;
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(IT_THREADS) k_integrate_velocities(uint32_t n,
     if (i >= n) return;
     uint4 mt = meta[i];
     uint32_t mode = mt.x & 0xffu, flags = mt.x >> 8;
-    if (mode < MODE_RIGID || !(flags & BF_ACTIVE)) return; // kinematic motion is applied by the host-side setter
+    if (mode < MODE_RIGID || !(flags & BF_ACTIVE) || (flags & BF_FROZEN)) return; // kinematic bodies: k_kinematic_velocities
     BodyVel v = vel[i];
     uint32_t locks = (flags >> BF_LOCK_SHIFT) & 63u;
     if (locks) {
@@ -259,7 +261,7 @@ __global__ void __launch_bounds__(IT_THREADS) k_ccd_forces(uint32_t n_ccd, const
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_ccd) return;
     uint32_t i = ids[t];
-    if (!((meta[i].x >> 8) & BF_ACTIVE)) return;
+    if (((meta[i].x >> 8) & (BF_ACTIVE | BF_FROZEN)) != BF_ACTIVE) return;
     V3 motion = f4v(vel[i].lin) * dt;
     ItemBox it = items[i];
     sweep_item(xf[i], shape_xf[i], shapes[shape_id[i]], motion, it, (int)npairs[i]);
@@ -276,7 +278,7 @@ __global__ void __launch_bounds__(IT_THREADS) k_kinematic_forces(uint32_t n_kin,
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_kin) return;
     uint32_t i = ids[t];
-    if (!((meta[i].x >> 8) & BF_ACTIVE)) return;
+    if (((meta[i].x >> 8) & (BF_ACTIVE | BF_FROZEN)) != BF_ACTIVE) return;
     BodyXf x = xf[i];
     KinState k = kin[i];
     V3 motion = f4v(k.target.o) - f4v(x.o);
@@ -297,15 +299,33 @@ __global__ void __launch_bounds__(IT_THREADS) k_kinematic_forces(uint32_t n_kin,
 // integrate_velocities of an active kinematic body (bradot_body_3d.cpp:700-708): it is where it was told to be; a body
 // that did not move goes back to sleep
 __global__ void __launch_bounds__(IT_THREADS) k_kinematic_velocities(uint32_t n_kin, const uint32_t *__restrict__ ids, BodyXf *__restrict__ xf,
-                                                                     const KinState *__restrict__ kin, const BodyVel *__restrict__ vel,
+                                                                     KinState *__restrict__ kin, BodyVel *__restrict__ vel,
                                                                      uint4 *__restrict__ meta) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_kin) return;
     uint32_t i = ids[t];
     uint4 mt = meta[i];
-    if (!((mt.x >> 8) & BF_ACTIVE)) return;
-    xf[i] = kin[i].target;
+    if (((mt.x >> 8) & (BF_ACTIVE | BF_FROZEN)) != BF_ACTIVE) return;
     BodyVel v = vel[i];
+    BodyXf nx = kin[i].target;
+    uint32_t locks = ((mt.x >> 8) >> BF_LOCK_SHIFT) & 63u;
+    if (locks) { // axis locks: velocities cleared, the locked origin components stay (bradot_body_3d.cpp:685-699)
+        BodyXf cur = xf[i];
+        for (int k = 0; k < 3; k++) {
+            if (locks & (1u << k)) {
+                (&v.lin.x)[k] = 0.f;
+                (&v.blin.x)[k] = 0.f;
+                (&nx.o.x)[k] = (&cur.o.x)[k];
+            }
+            if (locks & (1u << (k + 3))) {
+                (&v.ang.x)[k] = 0.f;
+                (&v.bang.x)[k] = 0.f;
+            }
+        }
+        vel[i] = v;
+        kin[i].target = nx;
+    }
+    xf[i] = nx;
     if (f4v(v.lin) == V3() && f4v(v.ang) == V3()) { // no contact reporting yet: contacts.size() == 0
         mt.x &= ~(BF_ACTIVE << 8);
         meta[i] = mt;
@@ -317,7 +337,7 @@ __global__ void __launch_bounds__(IT_THREADS) k_refresh_bodies(uint32_t first, u
                                                                BodyMassW *__restrict__ massw, const BodyProps *__restrict__ props,
                                                                const uint4 *__restrict__ meta, const BodyXf *__restrict__ shape_xf,
                                                                const uint32_t *__restrict__ shape_id, const ShapeRec *__restrict__ shapes,
-                                                               ItemBox *__restrict__ items) {
+                                                               ItemBox *__restrict__ items, const uint32_t *__restrict__ npairs) {
     uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= first + n) return;
     uint4 mt = meta[i];
@@ -327,14 +347,99 @@ __global__ void __launch_bounds__(IT_THREADS) k_refresh_bodies(uint32_t first, u
     BodyMassW mw = massw[i];
     transform_dependent(B, props[i], mode, mw);
     massw[i] = mw;
-    if (pass < 0) return; // mass data only
+    if (pass == -1) return; // mass data only
     ItemBox it = items[i];
     if (pass == 0) {
         it.cache_pos = make_float4(0.f, 0.f, 0.f, 0.f);
         it.cache_size = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    update_item(X3(B, f4v(x.o)), shape_xf[i], shapes[shape_id[i]], it, 0, pass == 0);
+    update_item(X3(B, f4v(x.o)), shape_xf[i], shapes[shape_id[i]], it, pass == -2 ? (int)npairs[i] : 0, pass == 0);
     items[i] = it;
+}
+
+// ---- body_set_state with the reference's side effects (bradot_body_3d.cpp:352-417)
+__global__ void k_set_state(SetStateArgs a) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= a.n) return;
+    uint32_t i = a.slots[t];
+    uint4 mt = a.meta[i];
+    uint32_t mode = mt.x & 0xffu, flags = mt.x >> 8;
+    if (flags & BF_FROZEN && mode == MODE_STATIC && mt.y == 0 && mt.z == 0) return; // tombstone of a destroyed body
+    bool wake = false;
+    switch (a.state) {
+        case BPC_STATE_TRANSFORM: {
+            const float *f = a.values + (size_t)t * 12;
+            BodyXf x;
+            x.r0 = make_float4(f[0], f[1], f[2], 0.f);
+            x.r1 = make_float4(f[3], f[4], f[5], 0.f);
+            x.r2 = make_float4(f[6], f[7], f[8], 0.f);
+            x.o = make_float4(f[9], f[10], f[11], 0.f);
+            if (mode == MODE_KINEMATIC) {
+                a.kin[i].target = x;
+                a.meta[i].x = mt.x | (BF_ACTIVE << 8); // set_active(true), bradot_body_3d.cpp:358
+                return;
+            }
+            if (mode >= MODE_RIGID) {
+                M3 B = orthonormalized(M3(f4v(x.r0), f4v(x.r1), f4v(x.r2)));
+                x.r0 = v4(B.r[0], 0.f);
+                x.r1 = v4(B.r[1], 0.f);
+                x.r2 = v4(B.r[2], 0.f);
+                BodyXf cur = a.xf[i];
+                bool same = f4v(cur.r0) == f4v(x.r0) && f4v(cur.r1) == f4v(x.r1) && f4v(cur.r2) == f4v(x.r2) && f4v(cur.o) == f4v(x.o);
+                wake = true;
+                if (same) break; // "if (new_transform == t) break" -- the switch, not the wakeup below it
+            } else {
+                atomicOr(&a.moved_static[i >> 5], 1u << (i & 31));
+            }
+            a.xf[i] = x;
+            {
+                BodyMassW mw = a.massw[i];
+                transform_dependent(M3(f4v(x.r0), f4v(x.r1), f4v(x.r2)), a.props[i], mode, mw);
+                a.massw[i] = mw;
+                ItemBox it = a.items[i];
+                update_item(X3(M3(f4v(x.r0), f4v(x.r1), f4v(x.r2)), f4v(x.o)), a.shape_xf[i], a.shapes[a.shape_id[i]], it, (int)a.npairs[i], false);
+                a.items[i] = it;
+            }
+        } break;
+        case BPC_STATE_LINEAR_VELOCITY:
+        case BPC_STATE_ANGULAR_VELOCITY: {
+            const float *f = a.values + (size_t)t * 3;
+            float4 v = make_float4(f[0], f[1], f[2], 0.f);
+            if (a.state == BPC_STATE_LINEAR_VELOCITY) a.vel[i].lin = v;
+            else a.vel[i].ang = v;
+            if (mode == MODE_KINEMATIC) {
+                if (a.state == BPC_STATE_LINEAR_VELOCITY) a.kin[i].clin = v;
+                else a.kin[i].cang = v;
+            }
+            wake = true;
+        } break;
+        case BPC_STATE_SLEEPING: {
+            if (mode < MODE_RIGID) return;
+            if (a.values[t] != 0.f) {
+                a.vel[i].lin = make_float4(0.f, 0.f, 0.f, 0.f);
+                a.vel[i].ang = make_float4(0.f, 0.f, 0.f, 0.f);
+                a.meta[i].x = mt.x & ~(BF_ACTIVE << 8);
+                return;
+            }
+            wake = true;
+        } break;
+        case BPC_STATE_CAN_SLEEP: {
+            bool cs = a.values[t] != 0.f;
+            uint32_t nf = cs ? (flags | BF_CAN_SLEEP) : (flags & ~BF_CAN_SLEEP);
+            if (mode >= MODE_RIGID && !(flags & BF_ACTIVE) && !cs) nf |= BF_ACTIVE;
+            a.meta[i].x = (mt.x & 0xff0000ffu) | ((nf & 0xffffu) << 8);
+            return;
+        }
+    }
+    // wakeup(): static and kinematic bodies are left alone (bradot_body_3d.h:287-292)
+    if (wake && mode >= MODE_RIGID && !(flags & BF_ACTIVE)) a.meta[i].x = mt.x | (BF_ACTIVE << 8);
+}
+
+
+int bpc_launch_set_state(bpc_context *ctx, const SetStateArgs &a) {
+    k_set_state<<<(a.n + 127) / 128, 128, 0, ctx->stream>>>(a);
+    BPC_CHECK(cudaGetLastError());
+    return 0;
 }
 
 // ---- sleep: per island "all sleepy" (bradot_step_3d.cpp:162-184) ------------------------------
@@ -427,13 +532,13 @@ int bpc_launch_integrate_velocities(bpc_context *ctx, float dt) {
 int bpc_launch_refresh_bodies(bpc_context *ctx, uint32_t first, uint32_t n, int passes) {
     if (!n) return 0;
     if (passes < 0) {
-        k_refresh_bodies<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(first, n, -1, ctx->xf.p, ctx->massw.p, ctx->props.p, ctx->meta.p,
-                                                                              ctx->shape_xf.p, ctx->shape_id.p, ctx->shapes.p, ctx->items.p);
+        k_refresh_bodies<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(first, n, passes, ctx->xf.p, ctx->massw.p, ctx->props.p, ctx->meta.p,
+                                                                              ctx->shape_xf.p, ctx->shape_id.p, ctx->shapes.p, ctx->items.p, ctx->npairs.p);
     }
     for (int pass = 0; pass < passes; pass++) {
         k_refresh_bodies<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(first, n, pass, ctx->xf.p, ctx->massw.p, ctx->props.p,
                                                                               ctx->meta.p, ctx->shape_xf.p, ctx->shape_id.p, ctx->shapes.p,
-                                                                              ctx->items.p);
+                                                                              ctx->items.p, ctx->npairs.p);
     }
     BPC_CHECK(cudaGetLastError());
     return 0;

@@ -397,3 +397,45 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
     BPC_CHECK(cudaGetLastError());
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Test hook: the device restatements of Geometry3D::get_closest_points_between_segments / get_closest_point_to_segment
+// (core/math/geometry_3d.h:86-129, 331-348) run on the reference's own test vectors (tests/core/math/test_geometry_3d.h).
+__global__ void k_test_segment_math(int op, uint32_t n, const float *__restrict__ in, float *__restrict__ out) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    if (op == 0) {
+        const float *f = in + (size_t)t * 12;
+        V3 ps, qt;
+        closest_points_between_segments(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8]), V3(f[9], f[10], f[11]), ps, qt);
+        float *o = out + (size_t)t * 6;
+        o[0] = ps.x; o[1] = ps.y; o[2] = ps.z; o[3] = qt.x; o[4] = qt.y; o[5] = qt.z;
+    } else {
+        const float *f = in + (size_t)t * 9;
+        V3 r = closest_point_to_segment(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8]));
+        float *o = out + (size_t)t * 3;
+        o[0] = r.x; o[1] = r.y; o[2] = r.z;
+    }
+}
+
+extern "C" int bpc_test_segment_math(bpc_context *ctx, int op, int n, const float *in, float *out) {
+    if (!ctx) return -1;
+    if ((op != 0 && op != 1) || n < 0 || (n > 0 && (!in || !out))) {
+        ctx->err = "bpc_test_segment_math: bad arguments";
+        return -1;
+    }
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    size_t wi = op == 0 ? 12 : 9, wo = op == 0 ? 6 : 3;
+    ctx->staging.reserve((size_t)n * (wi + wo), false, ctx->stream);
+    if (!ctx->staging.p) {
+        ctx->err = "out of device memory";
+        return -1;
+    }
+    BPC_CHECK(cudaMemcpyAsync(ctx->staging.p, in, (size_t)n * wi * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    k_test_segment_math<<<(n + 127) / 128, 128, 0, ctx->stream>>>(op, (uint32_t)n, ctx->staging.p, ctx->staging.p + (size_t)n * wi);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaMemcpyAsync(out, ctx->staging.p + (size_t)n * wi, (size_t)n * wo * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    BPC_CHECK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}

@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_rays(QArgs a) {
     if (!done && a.n_tree == 1) {
         q_ray_candidate(a, __float_as_uint(a.leaf_min[0].w), begin, end, normal, best);
     } else if (!done && a.n_tree > 1) {
-        uint32_t stack[96];
+        uint32_t stack[128]; // as deep as the traversal of the step: key length plus the index tie-break
         int sp = 0;
         uint32_t node = 0;
         while (true) {
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_rays(QArgs a) {
             if (done) break;
             bool il = hit[0] && !(child[0] & Q_LEAF_BIT), ir = hit[1] && !(child[1] & Q_LEAF_BIT);
             if (il) {
-                if (ir && sp < 96) stack[sp++] = child[1];
+                if (ir && sp < 128) stack[sp++] = child[1];
                 node = child[0];
             } else if (ir) {
                 node = child[1];
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_points(PArgs a) {
     if (a.q.n_tree == 1) {
         q_point_candidate(a, __float_as_uint(a.q.leaf_min[0].w), p, r, cc);
     } else if (a.q.n_tree > 1) {
-        uint32_t stack[96];
+        uint32_t stack[128]; // as deep as the traversal of the step: key length plus the index tie-break
         int sp = 0;
         uint32_t node = 0;
         while (true) {
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_points(PArgs a) {
             }
             bool il = hit[0] && !(child[0] & Q_LEAF_BIT), ir = hit[1] && !(child[1] & Q_LEAF_BIT);
             if (il) {
-                if (ir && sp < 96) stack[sp++] = child[1];
+                if (ir && sp < 128) stack[sp++] = child[1];
                 node = child[0];
             } else if (ir) {
                 node = child[1];

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
     if (a.n_tree == 1) {
         qs_candidate(a, __float_as_uint(a.leaf_min[0].w), qs, qx, r, cc);
     } else if (a.n_tree > 1) {
-        uint32_t stack[96];
+        uint32_t stack[128]; // as deep as the traversal of the step: key length plus the index tie-break
         int sp = 0;
         uint32_t node = 0;
         while (true) {
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
             }
             bool il = hit[0] && !(child[0] & QS_LEAF_BIT), ir = hit[1] && !(child[1] & QS_LEAF_BIT);
             if (il) {
-                if (ir && sp < 96) stack[sp++] = child[1];
+                if (ir && sp < 128) stack[sp++] = child[1];
                 node = child[0];
             } else if (ir) {
                 node = child[1];
@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
     if (a.n_tree == 1) {
         qc_candidate(a, __float_as_uint(a.leaf_min[0].w), qs, qx, sink);
     } else if (a.n_tree > 1) {
-        uint32_t stack[96];
+        uint32_t stack[128]; // as deep as the traversal of the step: key length plus the index tie-break
         int sp = 0;
         uint32_t node = 0;
         while (true) {
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
             }
             bool il = hit[0] && !(child[0] & QS_LEAF_BIT), ir = hit[1] && !(child[1] & QS_LEAF_BIT);
             if (il) {
-                if (ir && sp < 96) stack[sp++] = child[1];
+                if (ir && sp < 128) stack[sp++] = child[1];
                 node = child[0];
             } else if (ir) {
                 node = child[1];

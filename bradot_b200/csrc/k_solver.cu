@@ -8,6 +8,8 @@
 //   modules/bradot_physics_3d/bradot_step_3d.cpp:121-160        _pre_solve_island / _solve_island
 #include <cooperative_groups.h>
 
+#include <algorithm>
+
 #include "np_segment.cuh"
 namespace cg = cooperative_groups;
 
@@ -38,7 +40,8 @@ struct SvArgs {
     SolveContact *sc;     // contact c of slot s at sc[c * sc_stride + s]: the first contacts of a sweep are one dense stream
     size_t sc_stride;
     const JointRec *joints;
-    const JointSetup *jsetup;
+    JointSetup *jsetup; // the solver keeps a hinge's accumulated limit impulse in it
+    uint32_t max_priority;
     // continuous collision detection only
     const BodyXf *shape_xf;
     const float4 *shape_p;
@@ -186,6 +189,9 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
         a.info[s] = make_uint4(ia, ib, 0u, k);
         return;
     }
+    const SpaceParams &space = a.spaces[a.meta[ia].w];
+    // each space sweeps its own number of times (SPACE_PARAM_SOLVER_ITERATIONS); a body pair has solver priority 1
+    const uint32_t sweeps = ((uint32_t)space.iterations << 24) | (1u << 20);
     BodyS A, B;
     float fA, fB, boA, boB;
     load_body(a, ia, cA, A, fA, boA);
@@ -193,7 +199,7 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
     BodyXf xa = a.xf[ia], xb = a.xf[ib];
     M3 bA(f4v(xa.r0), f4v(xa.r1), f4v(xa.r2)), bB(f4v(xb.r0), f4v(xb.r1), f4v(xb.r2));
     V3 offset_B = f4v(xb.o) - f4v(xa.o);
-    const float max_pen = a.spaces[a.meta[ia].w].max_penetration;
+    const float max_pen = space.max_penetration;
     const float bias = 0.8f; // literal in the reference; SPACE_PARAM_CONTACT_DEFAULT_BIAS is not consulted (bradot_body_pair_3d.cpp:344)
     float friction = fabsf(fminf(fA, fB));
     float cb = boA + boB;
@@ -252,14 +258,15 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
         if (cB) store_body(a, ib, B);
         atomicAdd(&a.counters[CNT_ACTIVE_CONTACTS], (uint32_t)n_active);
     }
-    a.info[s] = make_uint4(ia, ib, (uint32_t)count | (cA ? 0x200u : 0u) | (cB ? 0x400u : 0u) | (any ? 0x800u : 0u), k);
+    a.info[s] = make_uint4(ia, ib, (uint32_t)count | (cA ? 0x200u : 0u) | (cB ? 0x400u : 0u) | (any ? 0x800u : 0u) | sweeps, k);
 }
 
-__device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
+// `it` = sweep number, `round` = priority round (1 = the regular sweeps, bradot_step_3d.cpp:134-160)
+__device__ inline void solve_pair(const SvArgs &a, uint32_t s, int it, uint32_t round) {
     uint4 inf = a.info[s];
     // first contact record requested together with the info word: its latency overlaps the body gathers
     SolveContact first = a.sc[s];
-    if (!(inf.z & 0x800u)) return;
+    if (!(inf.z & 0x800u) || it >= (int)(inf.z >> 24) || round > 1u) return;
     uint32_t ia = inf.x, ib = inf.y;
     int count = inf.z & 0xffu;
     bool cA = inf.z & 0x200u, cB = inf.z & 0x400u;
@@ -349,12 +356,9 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Joints: pin and hinge (modules/bradot_physics_3d/joints/bradot_pin_joint_3d.cpp:53-141,
-// joints/bradot_hinge_joint_3d.cpp:110-344, joints/bradot_jacobian_entry_3d.h:56-77).  Parameters are
-// the reference defaults: pin bias 0.3, damping 1, no clamp; hinge bias 0.3, relaxation 1, no limit, no motor.
-#define JOINT_TAU 0.3f
-#define JOINT_DAMPING 1.0f
-#define JOINT_RELAXATION 1.0f
+// Joints: pin and hinge (modules/bradot_physics_3d/joints/bradot_pin_joint_3d.cpp:53-170,
+// joints/bradot_hinge_joint_3d.cpp:110-440, joints/bradot_jacobian_entry_3d.h:56-77) with their parameters and flags:
+// pin bias / damping / impulse clamp; hinge bias, angular limit (accumulated, clamped impulse), motor.
 
 // BradotJoint3D::plane_space (bradot_joint_3d.h:43-59); Math_SQRT12 is a double
 __device__ __forceinline__ void plane_space(V3 n, V3 &p, V3 &q) {
@@ -393,16 +397,37 @@ struct JsArgs {
     const uint32_t *island_flag;
 };
 
+// BradotJoint3D::atan2fast (bradot_joint_3d.h:61-74); Math_PI is a double: coeff_1 = (float)(pi / 4.0f)
+__device__ __forceinline__ float atan2fast(float y, float x) {
+    float coeff_1 = (float)(3.14159265358979323846264338327950288 / 4.0);
+    float coeff_2 = 3.0f * coeff_1;
+    float abs_y = fabsf(y);
+    float angle;
+    if (x >= 0.0f) {
+        float r = (x - abs_y) / (x + abs_y);
+        angle = coeff_1 - coeff_1 * r;
+    } else {
+        float r = (x + abs_y) / (abs_y - x);
+        angle = coeff_2 - coeff_1 * r;
+    }
+    return (y < 0.0f) ? -angle : angle;
+}
+
 __global__ void __launch_bounds__(128) k_joint_setup(JsArgs a) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= a.n) return;
     const JointRec jr = a.joints[j];
+    JointSetup s;
+    if (jr.flags & JF_DEAD) { // destroyed: never awake, never solved
+        memset(&s, 0, sizeof(s));
+        a.out[j] = s;
+        return;
+    }
     uint32_t ma = a.meta[jr.a].x & 0xffu, mb = a.meta[jr.b].x & 0xffu;
     bool dynA = ma > MODE_KINEMATIC, dynB = mb > MODE_KINEMATIC;
     uint32_t root = a.island[ma != MODE_STATIC ? jr.a : jr.b];
     bool awake = (ma != MODE_STATIC || mb != MODE_STATIC) && (a.island_flag[root] & 1u);
-    JointSetup s;
-    uint32_t flags = (dynA ? 1u : 0u) | (dynB ? 2u : 0u) | (awake ? 4u : 0u);
+    uint32_t flags = (dynA ? 1u : 0u) | (dynB ? 2u : 0u) | (awake ? 4u : 0u) | ((jr.flags & JF_ENABLE_MOTOR) ? 8u : 0u);
     BodyXf xa = a.xf[jr.a], xb = a.xf[jr.b];
     X3 XA(M3(f4v(xa.r0), f4v(xa.r1), f4v(xa.r2)), f4v(xa.o)), XB(M3(f4v(xb.r0), f4v(xb.r1), f4v(xb.r2)), f4v(xb.o));
     BodyMassW mwa = a.massw[jr.a], mwb = a.massw[jr.b];
@@ -418,10 +443,12 @@ __global__ void __launch_bounds__(128) k_joint_setup(JsArgs a) {
     V3 nrm[3];
     s.axis_a = make_float4(0.f, 0.f, 0.f, 0.f);
     s.axis_b = make_float4(0.f, 0.f, 0.f, 0.f);
+    s.lim = make_float4(0.f, 0.f, 0.f, 0.f);
     if (jr.type == 0) {
         nrm[0] = V3(1.f, 0.f, 0.f);
         nrm[1] = V3(0.f, 1.f, 0.f);
         nrm[2] = V3(0.f, 0.f, 1.f);
+        s.prm = make_float4(jr.prm[0], jr.prm[1], jr.prm[2], 0.f); // bias (tau), damping, impulse clamp
     } else {
         V3 relPos = pivB - pivA;
         if (is_zero_approx(length_squared(relPos))) nrm[0] = V3(1.0f, 0.f, 0.f);
@@ -430,8 +457,28 @@ __global__ void __launch_bounds__(128) k_joint_setup(JsArgs a) {
         // hinge axes: column 2 of the local frames; B's column is flipped by the joint's constructor
         V3 axA = xform(XA.b, V3(jr.fa[2], jr.fa[5], jr.fa[8]));
         V3 axB = xform(XB.b, V3(jr.fb[2] * -1.f, jr.fb[5] * -1.f, jr.fb[8] * -1.f));
-        s.axis_a = v4(axA, 0.f);
-        s.axis_b = v4(axB, 0.f);
+        // limit (bradot_hinge_joint_3d.cpp:190-210): where the hinge stands against [lower, upper]
+        float correction = 0.f, limit_sign = 0.f;
+        if ((jr.flags & JF_USE_LIMIT) && jr.prm[2] <= jr.prm[1]) {
+            V3 refAxis0 = xform(XA.b, V3(jr.fa[0], jr.fa[3], jr.fa[6]));
+            V3 refAxis1 = xform(XA.b, V3(jr.fa[1], jr.fa[4], jr.fa[7]));
+            V3 swingAxis = xform(XB.b, V3(jr.fb[1], jr.fb[4], jr.fb[7]));
+            float angle = atan2fast(dot(swingAxis, refAxis0), dot(swingAxis, refAxis1));
+            if (angle <= jr.prm[2]) {
+                correction = jr.prm[2] - angle;
+                limit_sign = 1.0f;
+            } else if (angle >= jr.prm[1]) {
+                correction = jr.prm[1] - angle;
+                limit_sign = -1.0f;
+            }
+        }
+        // m_kHinge = 1 / (denominator_A(axisA) + denominator_B(axisA)), world inverse inertia tensors (:212-214)
+        M3 iwA(f4v(mwa.i0), f4v(mwa.i1), f4v(mwa.i2)), iwB(f4v(mwb.i0), f4v(mwb.i1), f4v(mwb.i2));
+        float k_hinge = 1.0f / (dot(axA, xform_inv(iwA, axA)) + dot(axA, xform_inv(iwB, axA)));
+        s.axis_a = v4(axA, k_hinge);
+        s.axis_b = v4(axB, limit_sign);
+        s.lim = make_float4(correction, 0.f, jr.prm[6], jr.prm[7]); // correction, accumulated limit impulse, motor target, motor max
+        s.prm = make_float4(jr.prm[0], jr.prm[5], jr.prm[3], 0.f);  // bias (tau), relaxation, limit bias
     }
     float d[3];
     for (int i = 0; i < 3; i++) d[i] = jac_diag_inv(w2a, w2b, rel1, rel2, nrm[i], iiA, imA, iiB, imB);
@@ -448,8 +495,9 @@ __device__ __forceinline__ float ang_denominator(const BodyS &b, V3 axis) { // c
     return dot(axis, xform_inv(b.iinv, axis));
 }
 
-__device__ inline void solve_joint(const SvArgs &a, uint32_t s) {
+__device__ inline void solve_joint(const SvArgs &a, uint32_t s, int it, uint32_t round) {
     uint4 inf = a.info[s];
+    if (it >= (int)(inf.z >> 24) || round > ((inf.z >> 20) & 15u)) return;
     const JointSetup js = a.jsetup[inf.w];
     uint32_t flags = __float_as_uint(js.pa.w);
     if (!(flags & 4u)) return;
@@ -461,8 +509,10 @@ __device__ inline void solve_joint(const SvArgs &a, uint32_t s) {
     load_body(a, inf.y, true, B, f2, f3);
     V3 pA = f4v(js.pa), pB = f4v(js.pb), dpos = f4v(js.dpos);
     const float4 rows[3] = { js.n0, js.n1, js.n2 };
-    uint32_t type = inf.z >> 16;
+    uint32_t type = (inf.z >> 16) & 15u;
+    const float tau = js.prm.x;
     if (type == 0) { // pin: the relative velocity is re-read for every axis
+        const float damping = js.prm.y, clamp = js.prm.z;
         for (int i = 0; i < 3; i++) {
             V3 normal = f4v(rows[i]);
             float jinv = rows[i].w;
@@ -471,7 +521,11 @@ __device__ inline void solve_joint(const SvArgs &a, uint32_t s) {
             V3 vel = vel1 - vel2;
             float rel_vel = dot(normal, vel);
             float depth = -dot(dpos, normal);
-            float impulse = depth * JOINT_TAU / a.dt * jinv - JOINT_DAMPING * rel_vel * jinv;
+            float impulse = depth * tau / a.dt * jinv - damping * rel_vel * jinv;
+            if (clamp > 0) {
+                if (impulse < -clamp) impulse = -clamp;
+                if (impulse > clamp) impulse = clamp;
+            }
             V3 iv = normal * impulse;
             if (dynA) apply_impulse(A, iv, pA);
             if (dynB) apply_impulse(B, -iv, pB);
@@ -485,13 +539,14 @@ __device__ inline void solve_joint(const SvArgs &a, uint32_t s) {
             float jinv = rows[i].w;
             float rel_vel = dot(normal, vel);
             float depth = -dot(dpos, normal);
-            float impulse = depth * JOINT_TAU / a.dt * jinv - rel_vel * jinv;
+            float impulse = depth * tau / a.dt * jinv - rel_vel * jinv;
             V3 iv = normal * impulse;
             if (dynA) apply_impulse(A, iv, pA);
             if (dynB) apply_impulse(B, -iv, pB);
         }
+        const float relaxation = js.prm.y;
         V3 axisA = f4v(js.axis_a), axisB = f4v(js.axis_b);
-        V3 angVelA = A.ang, angVelB = B.ang;
+        V3 angVelA = A.ang, angVelB = B.ang; // sampled here; the limit and the motor below still see these values
         V3 aroundA = axisA * dot(axisA, angVelA);
         V3 aroundB = axisB * dot(axisB, angVelB);
         V3 angAorthog = angVelA - aroundA;
@@ -501,7 +556,7 @@ __device__ inline void solve_joint(const SvArgs &a, uint32_t s) {
         if (len > 0.00001f) {
             V3 normal = normalized(velrelOrthog);
             float denom = ang_denominator(A, normal) + ang_denominator(B, normal);
-            velrelOrthog *= (1.0f / denom) * JOINT_RELAXATION;
+            velrelOrthog *= (1.0f / denom) * relaxation;
         }
         V3 angularError = -cross(axisA, axisB) * (1.0f / a.dt);
         float len2 = length(angularError);
@@ -512,6 +567,30 @@ __device__ inline void solve_joint(const SvArgs &a, uint32_t s) {
         }
         if (dynA) A.ang += xform(A.iinv, -velrelOrthog + angularError);
         if (dynB) B.ang += xform(B.iinv, velrelOrthog - angularError);
+        const float k_hinge = js.axis_a.w, limit_sign = js.axis_b.w;
+        if (limit_sign != 0.f) { // m_solveLimit (bradot_hinge_joint_3d.cpp:298-317)
+            float amplitude = (dot(angVelB - angVelA, axisA) * relaxation + js.lim.x * (1.0f / a.dt) * js.prm.z) * limit_sign;
+            float impulseMag = amplitude * k_hinge;
+            float temp = a.jsetup[inf.w].lim.y;
+            float acc = fmaxf(temp + impulseMag, 0.0f);
+            a.jsetup[inf.w].lim.y = acc;
+            impulseMag = acc - temp;
+            V3 impulse = axisA * impulseMag * limit_sign;
+            if (dynA) A.ang += xform(A.iinv, impulse);
+            if (dynB) B.ang += xform(B.iinv, -impulse);
+        }
+        if (flags & 8u) { // motor (:319-341)
+            V3 velrel = aroundA - aroundB;
+            float projRelVel = dot(velrel, axisA);
+            float motor_relvel = js.lim.z - projRelVel;
+            float unclipped = k_hinge * motor_relvel;
+            float max_imp = js.lim.w;
+            float clipped = unclipped > max_imp ? max_imp : unclipped;
+            clipped = clipped < -max_imp ? -max_imp : clipped;
+            V3 motorImp = clipped * axisA;
+            if (dynA) A.ang += xform(A.iinv, motorImp + V3(0.f, 0.f, 0.f));
+            if (dynB) B.ang += xform(B.iinv, -motorImp - V3(0.f, 0.f, 0.f));
+        }
     }
     if (dynA) store_body(a, inf.x, A);
     if (dynB) store_body(a, inf.y, B);
@@ -519,7 +598,8 @@ __device__ inline void solve_joint(const SvArgs &a, uint32_t s) {
 
 __device__ inline void pre_solve_joint(const SvArgs &a, uint32_t s, uint32_t j) {
     const JointRec &jr = a.joints[j];
-    a.info[s] = make_uint4(jr.a, jr.b, 0x1000u | (jr.type << 16), j);
+    uint32_t iters = (uint32_t)a.spaces[a.meta[jr.a].w].iterations;
+    a.info[s] = make_uint4(jr.a, jr.b, 0x1000u | (jr.type << 16) | ((jr.priority & 15u) << 20) | (iters << 24), j);
 }
 
 __device__ inline void finish_pair(const SvArgs &a, uint32_t s) {
@@ -562,25 +642,29 @@ __global__ void __launch_bounds__(SV_THREADS) k_solve(SvArgs a) {
         }
         grid.sync();
     }
-    for (int it = 0; it < a.iterations; it++) {
-        for (uint32_t g = 0; g < ng; g++) {
-            uint32_t lo = a.group_start[g], hi = a.group_start[g + 1];
-            if (g == a.serial_group) {
-                if (tid == 0) {
-                    for (uint32_t s = lo; s < hi; s++) {
+    // `iterations` sweeps over everything, then again for the constraints of solver priority >= 2, >= 3, ...
+    // (bradot_step_3d.cpp:134-160); a constraint sits out the sweeps beyond its own space's iteration count
+    for (uint32_t round = 1; round <= a.max_priority; round++) {
+        for (int it = 0; it < a.iterations; it++) {
+            for (uint32_t g = 0; g < ng; g++) {
+                uint32_t lo = a.group_start[g], hi = a.group_start[g + 1];
+                if (g == a.serial_group) {
+                    if (tid == 0) {
+                        for (uint32_t s = lo; s < hi; s++) {
+                            uint32_t id = a.sched[s];
+                            if (id < a.n_pairs) solve_pair(a, s, it, round);
+                            else if (id != 0xffffffffu) solve_joint(a, s, it, round);
+                        }
+                    }
+                } else {
+                    for (uint32_t s = lo + tid; s < hi; s += nth) {
                         uint32_t id = a.sched[s];
-                        if (id < a.n_pairs) solve_pair(a, s);
-                        else if (id != 0xffffffffu) solve_joint(a, s);
+                        if (id < a.n_pairs) solve_pair(a, s, it, round);
+                        else if (id != 0xffffffffu) solve_joint(a, s, it, round);
                     }
                 }
-            } else {
-                for (uint32_t s = lo + tid; s < hi; s += nth) {
-                    uint32_t id = a.sched[s];
-                    if (id < a.n_pairs) solve_pair(a, s);
-                    else if (id != 0xffffffffu) solve_joint(a, s);
-                }
+                grid.sync();
             }
-            grid.sync();
         }
     }
     uint32_t total = a.group_start[ng];
@@ -663,7 +747,9 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     a.dt = dt;
     a.inv_dt = (float)(1.0 / (double)dt);
     a.max_bias_av = (float)((3.14159265358979323846 / 8) / (double)dt);
-    a.iterations = ctx->spaces.empty() ? 16 : ctx->spaces[0].iterations;
+    a.iterations = 1;
+    for (const SpaceParams &sp : ctx->spaces) a.iterations = std::max(a.iterations, sp.iterations);
+    a.max_priority = nj ? ctx->max_priority : 1u;
     a.counters = ctx->counters.p;
     int per_sm = 0;
     void *kernel = ctx->h_ccd_ids.empty() ? (void *)k_solve<false> : (void *)k_solve<true>;

@@ -45,6 +45,7 @@ class Scene:
         self.n_spaces = n_spaces
         self.dt = np.float32(dt)
         self.iterations = iterations
+        self.iter_step = 0   # space s sweeps iterations + s * iter_step times (SPACE_PARAM_SOLVER_ITERATIONS is per space)
         self.name = name
         self.shapes = np.zeros(0, SHAPE_DT)
         self.bodies = np.zeros(0, BODY_DT)
@@ -100,7 +101,7 @@ class Scene:
     # -- file I/O ---------------------------------------------------------------
     def write(self, path):
         hdr = struct.pack("<4sIIIIIIfI7I", b"BSCN", 2, self.n_spaces, len(self.shapes), len(self.bodies),
-                          len(self.joints), len(self.verts), float(self.dt), self.iterations, *([0] * 7))
+                          len(self.joints), len(self.verts), float(self.dt), self.iterations, self.iter_step, *([0] * 6))
         with open(path, "wb") as f:
             f.write(hdr)
             f.write(self.shapes.tobytes())
@@ -112,10 +113,11 @@ class Scene:
     def read(path):
         with open(path, "rb") as f:
             raw = f.read()
-        magic, ver, nsp, nsh, nb, nj, nv, dt, it = struct.unpack_from("<4sIIIIIIfI", raw, 0)
+        magic, ver, nsp, nsh, nb, nj, nv, dt, it, its = struct.unpack_from("<4sIIIIIIfII", raw, 0)
         assert magic == b"BSCN" and ver == 2
         off = struct.calcsize("<4sIIIIIIfI7I")
         sc = Scene(nsp, dt, it)
+        sc.iter_step = its
         sc.shapes = np.frombuffer(raw, SHAPE_DT, nsh, off).copy()
         off += nsh * SHAPE_DT.itemsize
         sc.bodies = np.frombuffer(raw, BODY_DT, nb, off).copy()
@@ -465,3 +467,137 @@ def pushed(n=24):
     flags = np.where(np.arange(n) % 5 == 4, 1, 1 | PUSH_FLAG).astype(np.uint32)
     sc.add_bodies(n, shape=shape, xf=xf, flags=flags, mass=1.5)
     return sc
+
+
+def hanging_chains(n_chains=12, chain_len=5, seed=5):
+    """Joint parameters, hinge limits and motors, solver priorities: chains of boxes hanging from static anchors in empty
+    space (the links are on no collision layer, so every island consists of joints only).  Chain c: links joined
+    alternately by hinge and pin, the top link pinned to the anchor.  Hinges with an even index use a limit of
+    [-0.35, 0.5] rad, every third one also runs a motor; pins with an index divisible by 3 carry their own bias / damping /
+    impulse clamp.  All joints of chain c have solver priority 2 when c % 3 == 2 (one priority per island: the reference
+    compacts its island lists in place between priority rounds, which a mixed island would not survive as a dump)."""
+    sc = Scene(name="hanging_chains_%d" % n_chains)
+    anchor = sc.add_shape(SHAPE_BOX, (0.1, 0.1, 0.1))
+    link = sc.add_shape(SHAPE_BOX, (0.1, 0.3, 0.15))
+    rng = np.random.default_rng(seed)
+    hinge_i = pin_i = 0
+    for c in range(n_chains):
+        x0 = c * 10.0
+        xa = IDENT12.copy()
+        xa[9], xa[10] = x0, 10.0
+        a = sc.add_bodies(1, mode=MODE_STATIC, shape=anchor, xf=xa, layer=0, mask=0)
+        xf = np.tile(IDENT12, (chain_len, 1))
+        xf[:, 9] = x0
+        xf[:, 10] = 10.0 - 0.45 - 0.7 * np.arange(chain_len)
+        lin = rng.uniform(-1.5, 1.5, (chain_len, 3)).astype(np.float32)
+        ang = rng.uniform(-2.0, 2.0, (chain_len, 3)).astype(np.float32)
+        first = sc.add_bodies(chain_len, shape=link, xf=xf, mass=0.5 + 0.25 * (c % 3), layer=0, mask=0, linvel=lin, angvel=ang, flags=0)
+        prio = 2 if c % 3 == 2 else 0
+        # anchor -- link 0: pin
+        fa, fb = IDENT12.copy(), IDENT12.copy()
+        fa[10], fb[10] = -0.1, 0.35
+        sc.add_joints(1, type=JOINT_PIN, body_a=a, body_b=first, flags=JOINT_NO_COLLIDE, fa=fa, fb=fb, priority=prio)
+        for k in range(chain_len - 1):
+            fa, fb = IDENT12.copy(), IDENT12.copy()
+            fa[10], fb[10] = -0.35, 0.35
+            if k % 2 == 0:
+                flags, prm = JOINT_NO_COLLIDE, HINGE_DEFAULTS.copy()
+                if hinge_i % 2 == 0:
+                    flags |= JOINT_USE_LIMIT | JOINT_HAS_PARAMS
+                    prm[1], prm[2] = 0.5, -0.35            # upper, lower
+                    prm[3], prm[5] = 0.4, 0.9              # limit bias, relaxation
+                if hinge_i % 3 == 0:
+                    flags |= JOINT_ENABLE_MOTOR | JOINT_HAS_PARAMS
+                    prm[6], prm[7] = 1.5, 0.05             # target velocity, max impulse
+                if hinge_i % 5 == 4:
+                    flags |= JOINT_HAS_PARAMS
+                    prm[0] = 0.45                          # bias
+                sc.add_joints(1, type=JOINT_HINGE, body_a=first + k, body_b=first + k + 1, flags=flags, fa=fa, fb=fb, params=prm, priority=prio)
+                hinge_i += 1
+            else:
+                flags, prm = JOINT_NO_COLLIDE, PIN_DEFAULTS.copy()
+                if pin_i % 3 == 0:
+                    flags |= JOINT_HAS_PARAMS
+                    prm[0], prm[1], prm[2] = 0.5, 0.8, 0.05
+                sc.add_joints(1, type=JOINT_PIN, body_a=first + k, body_b=first + k + 1, flags=flags, fa=fa, fb=fb, params=prm, priority=prio)
+                pin_i += 1
+    return sc
+
+
+def locks_and_damping(n=48, seed=9, on_plane=False):
+    """body_set_axis_lock and the body damp modes: tumbling mixed bodies, each with its own lock bits (every other body),
+    damping values and COMBINE / REPLACE modes; far apart in the air, or (on_plane) dropped on a plane from a small height."""
+    sc = Scene(name="locks_and_damping_%d" % n)
+    rng = np.random.default_rng(seed)
+    if on_plane:
+        sc.add_static_plane((0, 1, 0), 0.0)
+        pos = np.stack([(np.arange(n) % 8) * 2.5, 0.8 + 0.1 * (np.arange(n) % 3), (np.arange(n) // 8) * 2.5], -1)
+    else:
+        pos = np.stack([np.arange(n) * 5.0, np.full(n, 100.0), np.zeros(n)], -1)
+    first = _mixed_bodies(sc, rng, pos)
+    b = sc.bodies
+    idx = np.arange(n)
+    b["linvel"][first:] = rng.uniform(-2, 2, (n, 3)).astype(np.float32)
+    b["angvel"][first:] = rng.uniform(-3, 3, (n, 3)).astype(np.float32)
+    b["lin_damp"][first:] = rng.uniform(0.0, 0.8, n).astype(np.float32)
+    b["ang_damp"][first:] = rng.uniform(0.0, 1.5, n).astype(np.float32)
+    locks = np.where(idx % 2 == 0, rng.integers(1, 64, n), 0).astype(np.uint32)
+    flags = np.ones(n, np.uint32) | (locks << BODY_LOCK_SHIFT)
+    flags |= np.where(idx % 3 == 0, BODY_LIN_DAMP_REPLACE, 0).astype(np.uint32)
+    flags |= np.where(idx % 4 == 1, BODY_ANG_DAMP_REPLACE, 0).astype(np.uint32)
+    b["flags"][first:] = flags
+    return sc
+
+
+def scripted_events():
+    """body_set_state and free() at run time.  Boxes resting (and falling asleep) on the ground and on a static platform; the
+    script (`events` below, applied before the step of that number by both sides): a sleeping box is teleported upwards, the
+    platform is moved away from under its boxes (they are woken as its neighbours), a sleeping box is given a velocity, a
+    moving body is put to sleep, a box is told it may not sleep, bodies are freed."""
+    sc = Scene(name="scripted_events")
+    sc.add_static_plane((0, 1, 0), 0.0)                                   # body 0
+    slab = sc.add_shape(SHAPE_BOX, (2.0, 0.1, 0.6))
+    box = sc.add_shape(SHAPE_BOX, (0.25, 0.25, 0.25))
+    ball = sc.add_shape(SHAPE_SPHERE, (0.3,))
+    xs = IDENT12.copy()
+    xs[9], xs[10], xs[11] = 0.0, 1.0, 4.0
+    sc.add_bodies(1, mode=MODE_STATIC, shape=slab, xf=xs)                   # body 1: platform
+    n = 6
+    xf = np.tile(IDENT12, (n, 1))
+    xf[:, 9] = (np.arange(n) - 2.5) * 1.5
+    xf[:, 10] = 0.27
+    sc.add_bodies(n, shape=box, xf=xf, mass=1.0)                            # bodies 2..7 on the ground
+    xp = np.tile(IDENT12, (3, 1))
+    xp[:, 9] = np.array([-1.2, 0.0, 1.2])
+    xp[:, 10] = 1.1 + 0.26
+    xp[:, 11] = 4.0
+    sc.add_bodies(3, shape=box, xf=xp, mass=1.0)                            # bodies 8..10 on the platform
+    xb = IDENT12.copy()
+    xb[9], xb[10], xb[11] = 6.0, 0.31, 0.0
+    sc.add_bodies(1, shape=ball, xf=xb, mass=2.0, linvel=(-0.5, 0.0, 0.0))  # body 11: a rolling ball
+    return sc
+
+
+def scripted_events_script():
+    """(step, body, kind, 12 floats) records for scripted_events(); kinds as in oracle/ref_harness.cpp."""
+    ev = []
+
+    def add(step, body, kind, v):
+        row = np.zeros(12, np.float32)
+        row[:len(v)] = v
+        ev.append((step, body, kind, row))
+    up = IDENT12.copy()
+    up[0], up[2], up[6], up[8] = np.cos(0.3), np.sin(0.3), -np.sin(0.3), np.cos(0.3)   # turned about y, not quite orthonormal in float
+    up[9], up[10], up[11] = -2.25, 1.5, 0.0
+    add(70, 3, 0, up * np.float32(1.0005))          # teleport a sleeping box (scaled basis: it is orthonormalised on the way in)
+    moved = IDENT12.copy()
+    moved[9], moved[10], moved[11] = 0.0, 0.4, 4.0
+    add(80, 1, 0, moved)                             # the platform drops by 0.6: its boxes are woken and fall after it
+    add(90, 5, 1, (0.0, 3.0, 0.5))                   # a sleeping box is thrown upwards
+    add(90, 5, 2, (0.0, 2.0, 0.0))
+    add(95, 11, 4, (1.0,))                           # the rolling ball is put to sleep: its velocities are cleared
+    add(100, 6, 3, ())                               # free a sleeping box
+    add(100, 9, 3, ())                               # free a box that is falling / resting on the platform
+    add(110, 2, 5, (0.0,))                           # a sleeping box may no longer sleep: it wakes
+    add(120, 11, 4, (0.0,))                          # wake the ball again
+    return ev

@@ -31,12 +31,17 @@ SPACE_PARAM_BODY_TIME_TO_SLEEP, SPACE_PARAM_SOLVER_ITERATIONS = 6, 7
 SPACE_GRAVITY_X, SPACE_GRAVITY_Y, SPACE_GRAVITY_Z, SPACE_LINEAR_DAMP, SPACE_ANGULAR_DAMP = 100, 101, 102, 103, 104
 
 INFO_ACTIVE_OBJECTS, INFO_COLLISION_PAIRS, INFO_ISLAND_COUNT = 0, 1, 2  # PhysicsServer3D::ProcessInfo
+BODY_STATE_TRANSFORM, BODY_STATE_LINEAR_VELOCITY, BODY_STATE_ANGULAR_VELOCITY, BODY_STATE_SLEEPING, BODY_STATE_CAN_SLEEP = range(5)
+_STATE_WIDTH = {0: 12, 1: 3, 2: 3, 3: 1, 4: 1}
 
 EXPORTS = [
     "bpc_create", "bpc_destroy", "bpc_last_error", "bpc_set_stream", "bpc_space_create", "bpc_space_set_param",
     "bpc_shape_create", "bpc_shape_create_convex", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
     "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
+    "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
+    "bpc_bodies_set_state", "bpc_bodies_read_slots", "bpc_bodies_write_slots", "bpc_bodies_read_state", "bpc_reserve",
+    "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_test_segment_math",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
@@ -76,6 +81,20 @@ def load_library(path=LIB_PATH):
     lib.bpc_bodies_read.argtypes = [vp, ci, ci, ci, vp]
     lib.bpc_body_count.argtypes = [vp]
     lib.bpc_joints_create.argtypes = [vp, vp, ci]
+    lib.bpc_joints_write.argtypes = [vp, ci, ci, vp]
+    lib.bpc_joints_destroy.argtypes = [vp, ci, ci]
+    lib.bpc_joint_count.argtypes = [vp]
+    lib.bpc_space_set_active.argtypes = [vp, ci, ci]
+    lib.bpc_space_destroy.argtypes = [vp, ci]
+    lib.bpc_bodies_create_slots.argtypes = [vp, vp, ci, vp]
+    lib.bpc_bodies_destroy.argtypes = [vp, vp, ci]
+    lib.bpc_bodies_update.argtypes = [vp, vp, ci, vp, ci]
+    lib.bpc_bodies_set_state.argtypes = [vp, ci, vp, ci, vp]
+    lib.bpc_bodies_read_slots.argtypes = [vp, ci, vp, ci, vp]
+    lib.bpc_bodies_write_slots.argtypes = [vp, ci, vp, ci, vp]
+    lib.bpc_bodies_read_state.argtypes = [vp, ci, ci, vp]
+    lib.bpc_reserve.argtypes = [vp, ci, ci]
+    lib.bpc_test_segment_math.argtypes = [vp, ci, ci, vp, vp]
     lib.bpc_step.argtypes = [vp, cf]
     lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
     lib.bpc_space_intersect_points.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp, vp]
@@ -189,9 +208,75 @@ class PhysicsServerCUDA:
         v = np.ascontiguousarray(values, np.float32).reshape(-1, _FIELD_WIDTH[field])
         self._check(self.lib.bpc_bodies_write(self.ctx, field, first, len(v), _ptr(v)))
 
+    def bodies_create_slots(self, records):
+        """Create bodies, reusing the slots of destroyed ones first; returns their indices."""
+        rec = np.ascontiguousarray(records, scenes.BODY_DT)
+        slots = np.zeros(len(rec), np.int32)
+        self._check(self.lib.bpc_bodies_create_slots(self.ctx, _ptr(rec), len(rec), _ptr(slots)))
+        return slots
+
+    def bodies_destroy(self, slots):
+        """free(RID) of bodies (servers/physics_server_3d.h: free)."""
+        sl = np.ascontiguousarray(slots, np.int32).reshape(-1)
+        self._check(self.lib.bpc_bodies_destroy(self.ctx, _ptr(sl), len(sl)))
+
+    def bodies_update(self, slots, records, keep_state=True):
+        """body_set_mode / body_set_param / body_set_collision_layer ... on bodies that are already in a space."""
+        sl = np.ascontiguousarray(slots, np.int32).reshape(-1)
+        rec = np.ascontiguousarray(records, scenes.BODY_DT)
+        assert len(sl) == len(rec)
+        self._check(self.lib.bpc_bodies_update(self.ctx, _ptr(sl), len(sl), _ptr(rec), 1 if keep_state else 0))
+
+    def body_set_state(self, slots, state, values):
+        """body_set_state with the reference's side effects (wake-ups, orthonormalised transform, broadphase box)."""
+        sl = np.ascontiguousarray(slots, np.int32).reshape(-1)
+        v = np.ascontiguousarray(values, np.float32).reshape(len(sl), _STATE_WIDTH[state])
+        self._check(self.lib.bpc_bodies_set_state(self.ctx, int(state), _ptr(sl), len(sl), _ptr(v)))
+
+    def bodies_read_slots(self, field, slots):
+        sl = np.ascontiguousarray(slots, np.int32).reshape(-1)
+        out = np.zeros((len(sl), _FIELD_WIDTH[field]), np.float32)
+        self._check(self.lib.bpc_bodies_read_slots(self.ctx, field, _ptr(sl), len(sl), _ptr(out)))
+        return out
+
+    def bodies_write_slots(self, field, slots, values):
+        sl = np.ascontiguousarray(slots, np.int32).reshape(-1)
+        v = np.ascontiguousarray(values, np.float32).reshape(len(sl), _FIELD_WIDTH[field])
+        self._check(self.lib.bpc_bodies_write_slots(self.ctx, field, _ptr(sl), len(sl), _ptr(v)))
+
+    def bodies_read_state(self, first=0, n=None, out=None):
+        """(n, 19): transform, linear velocity, angular velocity, active flag of every body in one copy."""
+        n = self.body_count() - first if n is None else n
+        if out is None:
+            out = np.zeros((n, 19), np.float32)
+        self._check(self.lib.bpc_bodies_read_state(self.ctx, first, n, _ptr(out)))
+        return out
+
+    def test_segment_math(self, op, rows):
+        r = np.ascontiguousarray(rows, np.float32).reshape(-1, 12 if op == 0 else 9)
+        out = np.zeros((len(r), 6 if op == 0 else 3), np.float32)
+        self._check(self.lib.bpc_test_segment_math(self.ctx, int(op), len(r), _ptr(r), _ptr(out)))
+        return out
+
+    def reserve(self, bodies, pairs):
+        self._check(self.lib.bpc_reserve(self.ctx, int(bodies), int(pairs)))
+
+    def space_set_active(self, space, active):
+        self._check(self.lib.bpc_space_set_active(self.ctx, int(space), 1 if active else 0))
+
+    def space_destroy(self, space):
+        self._check(self.lib.bpc_space_destroy(self.ctx, int(space)))
+
     def joints_create(self, records):
         rec = np.ascontiguousarray(records, scenes.JOINT_DT)
         return self._check(self.lib.bpc_joints_create(self.ctx, _ptr(rec), len(rec)))
+
+    def joints_write(self, first, records):
+        rec = np.ascontiguousarray(records, scenes.JOINT_DT)
+        self._check(self.lib.bpc_joints_write(self.ctx, int(first), len(rec), _ptr(rec)))
+
+    def joints_destroy(self, first, n=1):
+        self._check(self.lib.bpc_joints_destroy(self.ctx, int(first), int(n)))
 
     # -- stepping -----------------------------------------------------------------------------
     def step(self, dt):
@@ -288,9 +373,9 @@ class PhysicsServerCUDA:
         """Build every space / shape / body / joint of a scenes.Scene.  ``meshes`` maps a convex
         shape index to its hull (Geometry3D::MeshData layout), e.g. the reference's own from an oracle dump; a convex
         shape without an entry gets its hull from bradot_b200.hull (same conventions, Qhull underneath)."""
-        for _ in range(sc.n_spaces):
+        for k in range(sc.n_spaces):
             sp = self.space_create()
-            self.space_set_param(sp, SPACE_PARAM_SOLVER_ITERATIONS, sc.iterations)
+            self.space_set_param(sp, SPACE_PARAM_SOLVER_ITERATIONS, sc.iterations + k * getattr(sc, "iter_step", 0))
         for i, s in enumerate(sc.shapes):
             if s["type"] == scenes.SHAPE_CONVEX:
                 if meshes is None or i not in meshes:

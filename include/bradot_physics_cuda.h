@@ -28,7 +28,10 @@ enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1 };
  * body_set_mode / body_add_shape / body_set_param / body_set_state / body_set_space
  * (P3D/bradot_physics_server_3d.cpp:438-760). */
 typedef struct bpc_body_desc {
-    uint32_t space, mode, shape, flags; /* flags: bit0 can_sleep, bit1 continuous collision detection, bit2 start asleep */
+    /* flags: bit0 can_sleep, bit1 continuous collision detection, bit2 start asleep, bit4 / bit5 linear / angular damp mode
+     * REPLACE (BODY_PARAM_*_DAMP_MODE, P3D/bradot_body_3d.cpp:586-606), bit6 omit force integration, bits 8..13 axis locks
+     * in PhysicsServer3D::BodyAxis order (body_set_axis_lock, P3D/bradot_body_3d.cpp:685-699) */
+    uint32_t space, mode, shape, flags;
     float xf[12];                       /* basis rows (9) then origin (3) */
     float shape_xf[12];                 /* local transform of the single shape */
     float linvel[3], angvel[3];
@@ -37,8 +40,17 @@ typedef struct bpc_body_desc {
 } bpc_body_desc;
 
 typedef struct bpc_joint_desc {
-    uint32_t type, body_a, body_b, flags; /* flags bit0: bodies do not collide with each other */
-    float frame_a[12], frame_b[12];       /* pin: origins only (local anchors); hinge: local frames */
+    /* flags: bit0 the two bodies do not collide with each other (joint_disable_collisions_between_bodies), bit1 hinge
+     * HINGE_JOINT_FLAG_USE_LIMIT, bit2 hinge HINGE_JOINT_FLAG_ENABLE_MOTOR, bit3 `params` holds values (otherwise the
+     * reference's defaults: pin 0.3 / 1 / 0, hinge P3D/joints/bradot_hinge_joint_3d.h:73-88) */
+    uint32_t type, body_a, body_b, flags;
+    float frame_a[12], frame_b[12]; /* pin: origins only (local anchors); hinge: local frames */
+    /* pin: PinJointParam order (bias, damping, impulse clamp; P3D/joints/bradot_pin_joint_3d.cpp:143-155); hinge:
+     * HingeJointParam order (bias, limit upper, limit lower, limit bias, limit softness, limit relaxation, motor target
+     * velocity, motor max impulse; P3D/joints/bradot_hinge_joint_3d.cpp:362-392) */
+    float params[8];
+    uint32_t priority; /* joint_set_solver_priority (P3D/bradot_physics_server_3d.cpp:1376): 0 or 1 = default */
+    uint32_t reserved[3];
 } bpc_joint_desc;
 
 /* PhysicsServer3D::SpaceParameter (servers/physics_server_3d.h:283-292) plus the default-area
@@ -90,9 +102,14 @@ const char *bpc_last_error(bpc_context *ctx);
 /* CUDA stream all work is enqueued on (cudaStream_t as void*); 0 = default stream. */
 int bpc_set_stream(bpc_context *ctx, void *cuda_stream);
 
-/* ---- spaces: space_create / space_set_param (P3D/bradot_physics_server_3d.cpp:144-191) */
+/* ---- spaces: space_create / space_set_param / space_set_active / free(space) (P3D/bradot_physics_server_3d.cpp:144-191,
+ * 1603-1611).  Each space has its own solver iteration count (1..255).  An inactive space is not stepped: its bodies keep
+ * their state and their cached pairs and are not counted by bpc_get_stats.  Destroying a space destroys its bodies and their joints; its index is
+ * not reused. */
 int bpc_space_create(bpc_context *ctx);
 int bpc_space_set_param(bpc_context *ctx, int space, int param, float value);
+int bpc_space_set_active(bpc_context *ctx, int space, int active);
+int bpc_space_destroy(bpc_context *ctx, int space);
 
 /* ---- shapes: shape_create + shape_set_data (P3D/bradot_physics_server_3d.cpp:50-142; P3D/bradot_shape_3d.cpp _setup) */
 int bpc_shape_create(bpc_context *ctx, int type, const float params[4]);
@@ -108,10 +125,54 @@ int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, int n); /* r
 int bpc_bodies_write(bpc_context *ctx, int field, int first, int n, const float *host);
 int bpc_bodies_read(bpc_context *ctx, int field, int first, int n, float *host);
 int bpc_body_count(bpc_context *ctx);
+/* Like bpc_bodies_create, but slots of destroyed bodies are handed out first (most recently freed first, as the reference's
+ * PooledList does for broadphase ids, core/templates/pooled_list.h:100-121); slots_out receives one body index per record. */
+int bpc_bodies_create_slots(bpc_context *ctx, const bpc_body_desc *descs, int n, int32_t *slots_out);
+/* free(RID) of a body (P3D/bradot_physics_server_3d.cpp:1572-1590): the body leaves the broadphase, its pairs are gone with
+ * the next step, joints attached to it are destroyed with it.  As in the reference, nothing is woken (the body is unpaired
+ * before its shapes go, so wakeup_neighbours finds no neighbours): a sleeping body resting on a freed one sleeps on.
+ * Slots stay valid indices (reads return the tombstone) until reused. */
+int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n);
+/* Re-describe existing bodies: everything body_set_mode / body_set_param / body_set_collision_layer|mask / body_set_shape /
+ * body_set_axis_lock / body_set_enable_continuous_collision_detection change after a body is in a space
+ * (P3D/bradot_physics_server_3d.cpp:479-760).  keep_state != 0: the records' transform and velocities are ignored, the
+ * body keeps the ones it has (and its sleep state, unless the new mode forbids it). */
+int bpc_bodies_update(bpc_context *ctx, const int32_t *slots, int n, const bpc_body_desc *descs, int keep_state);
+
+/* body_set_state with the reference's side effects (BradotBody3D::set_state, P3D/bradot_body_3d.cpp:352-417), for a list
+ * of bodies.  The BPC_FIELD_* writes above restore raw state (snapshots, tests) and have none of these side effects.
+ *   BPC_STATE_TRANSFORM        12 floats.  Rigid: orthonormalised, mass data and broadphase box follow (the box through the
+ *                              usual hysteresis, as a move), the body wakes.  Static: placed, bodies it touches are woken.
+ *                              Kinematic: becomes the target of the next step (= BPC_FIELD_KINEMATIC_TARGET).
+ *   BPC_STATE_LINEAR_VELOCITY  3 floats; wakes the body (kinematic: its constant velocity)
+ *   BPC_STATE_ANGULAR_VELOCITY 3 floats; wakes the body
+ *   BPC_STATE_SLEEPING         1 float (0/1); rigid bodies only; going to sleep zeroes the velocities
+ *   BPC_STATE_CAN_SLEEP        1 float (0/1); clearing it wakes a sleeping rigid body
+ * Numeric values are PhysicsServer3D::BodyState (servers/physics_server_3d.h:472-478). */
+enum { BPC_STATE_TRANSFORM = 0, BPC_STATE_LINEAR_VELOCITY = 1, BPC_STATE_ANGULAR_VELOCITY = 2, BPC_STATE_SLEEPING = 3, BPC_STATE_CAN_SLEEP = 4 };
+int bpc_bodies_set_state(bpc_context *ctx, int state, const int32_t *slots, int n, const float *values);
+/* Gather / scatter variants of the bulk I/O for a list of bodies (state sync of the active bodies only, forces of the pushed
+ * bodies only): one staging copy and one kernel whatever n is. */
+int bpc_bodies_read_slots(bpc_context *ctx, int field, const int32_t *slots, int n, float *host);
+int bpc_bodies_write_slots(bpc_context *ctx, int field, const int32_t *slots, int n, const float *host);
+/* Transform (12), linear velocity (3), angular velocity (3), active (1) of every body in one call: 19 floats per body. */
+int bpc_bodies_read_state(bpc_context *ctx, int first, int n, float *host);
+
+/* Size every per-body and per-pair buffer for `bodies` bodies and `pairs` broadphase pairs up front, so that bpc_step does
+ * not allocate while the counts stay below them (a pair burst beyond `pairs` still grows the buffers, once). */
+int bpc_reserve(bpc_context *ctx, int bodies, int pairs);
 
 /* ---- joints: joint_make_pin / joint_make_hinge / joint_disable_collisions_between_bodies
  * (P3D/bradot_physics_server_3d.cpp:1224-1246, 1388-1406) */
 int bpc_joints_create(bpc_context *ctx, const bpc_joint_desc *descs, int n);
+/* pin_joint_set_param / hinge_joint_set_param / hinge_joint_set_flag / joint_set_solver_priority /
+ * joint_disable_collisions_between_bodies at run time (P3D/bradot_physics_server_3d.cpp:1248-1406): rewrite n joint records
+ * starting at `first`; type and bodies must stay what they are. */
+int bpc_joints_write(bpc_context *ctx, int first, int n, const bpc_joint_desc *descs);
+/* joint_clear / free(joint) (P3D/bradot_physics_server_3d.cpp:1229-1246, 1592-1601): the joint stops acting, the collision
+ * exception it made is dropped; indices of other joints do not move. */
+int bpc_joints_destroy(bpc_context *ctx, int first, int n);
+int bpc_joint_count(bpc_context *ctx);
 
 /* ---- the step: BradotPhysicsServer3D::step -> BradotStep3D::step for every space at once
  * (P3D/bradot_physics_server_3d.cpp:1632-1648, P3D/bradot_step_3d.cpp:186-410) */
@@ -181,6 +242,12 @@ int bpc_space_collide_shapes(bpc_context *ctx, int space, int n, const int32_t *
 /* ---- utilities exposed for tests and tools */
 /* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */
 int bpc_sort_u64(bpc_context *ctx, const uint64_t *keys_in, uint64_t *keys_out, int n);
+
+/* The device forms of Geometry3D::get_closest_points_between_segments (op 0: 12 floats p0 p1 q0 q1 -> 6 floats ps qt) and
+ * Geometry3D::get_closest_point_to_segment (op 1: 9 floats point s0 s1 -> 3 floats), which the capsule routines use
+ * (core/math/geometry_3d.h:86-129, 331-348); the tests run the reference's own vectors through them
+ * (tests/core/math/test_geometry_3d.h:39-48, 133). */
+int bpc_test_segment_math(bpc_context *ctx, int op, int n, const float *in, float *out);
 
 /* Allocation-free variant of the key sort.  It has no counterpart in the reference; it exists for
  * hosts that hand over device buffers of their own and may not cause a cudaMalloc / cudaFree while

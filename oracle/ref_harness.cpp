@@ -11,7 +11,8 @@
 //   modules/bradot_physics_3d/bradot_physics_server_3d.cpp:1632  BradotPhysicsServer3D::step
 //   modules/bradot_physics_3d/bradot_step_3d.cpp:186              BradotStep3D::step
 //
-// usage: oracle_step <scene.bscn> [--steps N] [--dump out.bdmp] [--dump-from A] [--dump-every K] [--rays rays.bin]
+// usage: oracle_step <scene.bscn> [--steps N] [--dump out.bdmp] [--dump-from A] [--dump-every K | --dump-steps a,b,c]
+//                    [--slim] [--rays rays.bin]
 //   rays.bin: uint32 n, then n x (from xyz, to xyz) float32; every dumped step also holds "rays" (n,8): hit, body
 //   index, position xyz, normal xyz of PhysicsDirectSpaceState3D::intersect_ray in space 0 (mask 0xffffffff), and
 //   "points" (n,9): count and up to 8 body indices of intersect_point at each ray's origin
@@ -20,7 +21,8 @@
 //   to every non-static body through body_set_state after the scene is built (a settled state handed over by the other
 //   side, so that the CPU run does not pay for settling it again).
 //   events.bin: uint32 n, then n x (int32 step, int32 body, int32 kind, float32[12]): applied before the step of that
-//   number.  kind 0 body_set_state(TRANSFORM), 1 LINEAR_VELOCITY, 2 ANGULAR_VELOCITY, 3 free(body), 4 SLEEPING(v[0] != 0).
+//   number.  kind 0 body_set_state(TRANSFORM), 1 LINEAR_VELOCITY, 2 ANGULAR_VELOCITY, 3 free(body), 4 SLEEPING(v[0] != 0),
+//   5 CAN_SLEEP(v[0] != 0).
 // Scenes with several spaces are stepped space by space with the reference's own stepper (what BradotPhysicsServer3D::step
 // does, bradot_physics_server_3d.cpp:1632-1648) whenever a dump is written, so that each space's sweep order can be recorded.
 // Timing JSON goes to stdout (one line).
@@ -45,6 +47,7 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -68,7 +71,8 @@ struct ScnHeader {
 	uint32_t n_spaces, n_shapes, n_bodies, n_joints, n_verts;
 	float dt;
 	uint32_t iterations;
-	uint32_t reserved[7];
+	uint32_t iter_step; // space s sweeps iterations + s * iter_step times
+	uint32_t reserved[6];
 };
 struct ScnShape {
 	uint32_t type; // PhysicsServer3D::ShapeType
@@ -158,6 +162,7 @@ struct World {
 	std::vector<std::pair<int, const BradotConstraint3D *>> last_order;
 	int32_t last_stats[4] = { 0, 0, 0, 0 };
 	bool order_valid = false;
+	bool slim = false; // --slim: contact records only for the pairs that hold contacts ("contacts_idx" names them)
 };
 
 // One tick.  With `record`: what BradotPhysicsServer3D::step does (bradot_physics_server_3d.cpp:1632-1648), space by space
@@ -246,6 +251,7 @@ static void dump_step(Dump &d, World &w, int step) {
 	std::vector<int32_t> pi;
 	std::vector<float> pf;
 	std::vector<float> cf;
+	std::vector<int32_t> cidx;
 	std::map<const BradotConstraint3D *, int> pair_index;
 	for (int i = 0; i < nb; i++) {
 		if (w.body_freed[i]) {
@@ -264,6 +270,12 @@ static void dump_step(Dump &d, World &w, int step) {
 			pi.push_back((p->collided ? 1 : 0) | (p->collide_A ? 2 : 0) | (p->collide_B ? 4 : 0) | (p->check_ccd ? 8 : 0));
 			put3(pf, p->sep_axis);
 			put3(pf, p->offset_B);
+			if (w.slim) {
+				if (p->contact_count == 0) {
+					continue;
+				}
+				cidx.push_back((int32_t)(pi.size() / 4 - 1));
+			}
 			for (int c = 0; c < 4; c++) {
 				const BradotBodyPair3D::Contact &ct = p->contacts[c];
 				size_t base = cf.size();
@@ -292,7 +304,12 @@ static void dump_step(Dump &d, World &w, int step) {
 	uint64_t np = pi.size() / 4;
 	d.arr("pair_ids", step, "i4", { np, 4 }, pi.data(), pi.size() * 4);
 	d.arr("pair_f", step, "f4", { np, 6 }, pf.data(), pf.size() * 4);
-	d.arr("contacts", step, "f4", { np, 4, CONTACT_STRIDE }, cf.data(), cf.size() * 4);
+	if (w.slim) {
+		d.arr("contacts_idx", step, "i4", { (uint64_t)cidx.size() }, cidx.data(), cidx.size() * 4);
+		d.arr("contacts", step, "f4", { (uint64_t)cidx.size(), 4, CONTACT_STRIDE }, cf.data(), cf.size() * 4);
+	} else {
+		d.arr("contacts", step, "f4", { np, 4, CONTACT_STRIDE }, cf.data(), cf.size() * 4);
+	}
 
 	// solve order actually used this step: after _pre_solve_island/_solve_island the island vectors
 	// hold the constraints that were solved, in sweep order (bradot_step_3d.cpp:121-160); step_world noted them.
@@ -549,6 +566,8 @@ int main(int argc, char **argv) {
 	const char *scene_path = argv[1];
 	int steps = 1, dump_from = 0, dump_every = 1, threads = -1, warmup = 0;
 	const char *dump_path = nullptr, *rays_path = nullptr, *state_path = nullptr, *events_path = nullptr;
+	bool slim = false;
+	std::set<int> dump_steps;
 	for (int i = 2; i < argc; i++) {
 		std::string a = argv[i];
 		if (a == "--steps") {
@@ -569,6 +588,12 @@ int main(int argc, char **argv) {
 			state_path = argv[++i];
 		} else if (a == "--events") {
 			events_path = argv[++i];
+		} else if (a == "--slim") {
+			slim = true;
+		} else if (a == "--dump-steps") { // comma-separated step numbers: dump exactly these (overrides --dump-from / --dump-every)
+			for (char *tok = strtok(argv[++i], ","); tok; tok = strtok(nullptr, ",")) {
+				dump_steps.insert(atoi(tok));
+			}
 		}
 	}
 
@@ -623,6 +648,7 @@ int main(int argc, char **argv) {
 	(void)globals;
 
 	World w;
+	w.slim = slim;
 	w.ps = memnew(BradotPhysicsServer3D(false));
 	w.ps->init();
 	BradotPhysicsServer3D *ps = w.ps;
@@ -630,7 +656,7 @@ int main(int argc, char **argv) {
 	for (uint32_t i = 0; i < hd.n_spaces; i++) {
 		RID sp = ps->space_create();
 		ps->space_set_active(sp, true);
-		ps->space_set_param(sp, PhysicsServer3D::SPACE_PARAM_SOLVER_ITERATIONS, hd.iterations);
+		ps->space_set_param(sp, PhysicsServer3D::SPACE_PARAM_SOLVER_ITERATIONS, hd.iterations + i * hd.iter_step);
 		w.spaces.push_back(sp);
 	}
 	for (uint32_t i = 0; i < hd.n_shapes; i++) {
@@ -807,7 +833,7 @@ int main(int argc, char **argv) {
 	}
 	if (d.f) {
 		dump_meshes(d, w);
-		if (dump_from <= 0) {
+		if (dump_steps.empty() ? dump_from <= 0 : dump_steps.count(0) > 0) {
 			dump_step(d, w, 0);
 		}
 	}
@@ -841,18 +867,22 @@ int main(int argc, char **argv) {
 				case 4:
 					ps->body_set_state(body, PhysicsServer3D::BODY_STATE_SLEEPING, e.v[0] != 0.f);
 					break;
+				case 5:
+					ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, e.v[0] != 0.f);
+					break;
 			}
 		}
 		drive_kinematic(d, w, s, hd.dt, true);
 		push_bodies(w, w.body_flags);
-		step_world(w, hd.dt, record && s >= dump_from - 1);
+		const bool dump_this = dump_steps.empty() ? (s >= dump_from && ((s - dump_from) % dump_every) == 0) : dump_steps.count(s) > 0;
+		step_world(w, hd.dt, record && dump_this);
 		for (RID sp : w.spaces) {
 			BradotSpace3D *space = ps->space_owner.get_or_null(sp);
 			for (int k = 0; k < 5; k++) {
 				phase_us[k] += space->get_elapsed_time((BradotSpace3D::ElapsedTime)k);
 			}
 		}
-		if (d.f && s >= dump_from && ((s - dump_from) % dump_every) == 0) {
+		if (d.f && dump_this) {
 			dump_step(d, w, s);
 			dump_rays(d, w, s, rays);
 		}

@@ -19,9 +19,14 @@ def have_oracle():
     return os.path.exists(ORACLE) and os.access(ORACLE, os.X_OK)
 
 
-def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays=None):
+EVENT_DT = np.dtype([("step", "<i4"), ("body", "<i4"), ("kind", "<i4"), ("v", "<f4", 12)])
+
+
+def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays=None, state=None, events=None, warmup=0, slim=False, dump_steps=None):
     """Step `sc` with the reference; returns (timing dict, dump dict).  `rays` (n, 6) float32 from/to: every dumped step
-    also holds ("rays", step) = the reference's intersect_ray answers in space 0."""
+    also holds ("rays", step) = the reference's intersect_ray answers in space 0.  `state` (n_bodies, 18): transforms and
+    velocities given to the moving bodies before the first step.  `events`: (step, body, kind, values) records applied before
+    the step of that number (oracle/ref_harness.cpp)."""
     d = tempfile.mkdtemp(prefix="bpc_oracle_")
     scn = os.path.join(d, "scene.bscn")
     dmp = keep or os.path.join(d, "out.bdmp")
@@ -36,7 +41,32 @@ def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays
             f.write(np.uint32(len(r6)).tobytes())
             f.write(r6.tobytes())
         cmd += ["--rays", rays_path]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=1200)
+    extra = []
+    if state is not None:
+        st = np.ascontiguousarray(state, np.float32).reshape(len(sc.bodies), 18)
+        extra.append(os.path.join(d, "state.bin"))
+        with open(extra[-1], "wb") as f:
+            f.write(np.uint32(len(st)).tobytes())
+            f.write(st.tobytes())
+        cmd += ["--state", extra[-1]]
+    if events is not None:
+        ev = np.zeros(len(events), EVENT_DT)
+        for i, (step, body, kind, v) in enumerate(events):
+            ev[i] = (step, body, kind, v)
+        extra.append(os.path.join(d, "events.bin"))
+        with open(extra[-1], "wb") as f:
+            f.write(np.uint32(len(ev)).tobytes())
+            f.write(ev.tobytes())
+        cmd += ["--events", extra[-1]]
+    if warmup:
+        cmd += ["--warmup", str(warmup)]
+    if slim:
+        cmd += ["--slim"]
+    if dump_steps is not None:
+        cmd += ["--dump-steps", ",".join(str(int(x)) for x in sorted(set(dump_steps)))]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=3000)
+    for e in extra:
+        os.remove(e)
     if rays_path:
         os.remove(rays_path)
     if r.returncode != 0:
@@ -57,12 +87,14 @@ def oracle_pairs(dump, step):
     c = dump[("contacts", step)]
     n = len(ids)
     cf = np.zeros((n, 4, 16), np.float32)
-    cf[:, :, 0:9] = c[:, :, 0:9]      # local_A, local_B, normal
-    cf[:, :, 9] = c[:, :, 10]         # acc_normal
-    cf[:, :, 10:13] = c[:, :, 11:14]  # acc_tangent
-    cf[:, :, 13] = c[:, :, 14]        # acc_bias
-    cf[:, :, 14] = c[:, :, 15]        # acc_bias_com
-    cf[:, :, 15] = c[:, :, 20]        # used
+    # a slim dump (--slim) holds contact records only for the pairs that have contacts
+    sel = dump[("contacts_idx", step)] if ("contacts_idx", step) in dump else slice(None)
+    cf[sel, :, 0:9] = c[:, :, 0:9]      # local_A, local_B, normal
+    cf[sel, :, 9] = c[:, :, 10]         # acc_normal
+    cf[sel, :, 10:13] = c[:, :, 11:14]  # acc_tangent
+    cf[sel, :, 13] = c[:, :, 14]        # acc_bias
+    cf[sel, :, 14] = c[:, :, 15]        # acc_bias_com
+    cf[sel, :, 15] = c[:, :, 20]        # used
     return ids, pf, cf
 
 
@@ -126,8 +158,8 @@ def teacher_forced(sc, steps, check_steps, import_order=True, dump=None):
 
     Step 0 -> 1 is never checked: the reference flushes its pending shape updates at the start of the
     first step (bradot_physics_server_3d.cpp:1728-1733), which re-stores every broadphase box before pairing."""
-    if dump is None:
-        _, dump = run_oracle(sc, steps, dump_from=0, dump_every=1)
+    if dump is None:   # only the steps that are loaded or compared are dumped
+        _, dump = run_oracle(sc, steps, dump_steps=[k for k in check_steps] + [k + 1 for k in check_steps], slim=True)
     ps = new_server(sc, dump)
     worst = {"contact": 0.0, "state": 0.0, "pairs": 0, "colliding": 0, "contacts": 0, "items": 0.0, "item_pairs_differ": 0}
     for k in check_steps:

@@ -1,0 +1,260 @@
+"""GPU parity tests of the smaller rows: joint parameters / hinge limits / motors / solver priorities (a15, a16), axis locks
+and body damp modes (a2, a7), per-space solver iterations (a16), body_set_state and free() at run time (boundary),
+inactive spaces, and the reference's own helper vectors (tests/core/math/test_geometry_3d.h).  The checker is the
+reference's own code (oracle/_ref/oracle_step)."""
+import numpy as np
+import pytest
+
+import parity
+from bradot_b200 import scenes, server
+
+pytestmark = pytest.mark.gpu
+
+STATE_TOL = 1e-4
+CONTACT_TOL = 1e-5
+
+
+def _need_oracle():
+    if not parity.have_oracle():
+        pytest.skip("oracle/_ref/oracle_step not built")
+
+
+def test_reference_segment_vectors_on_the_device():
+    """tests/core/math/test_geometry_3d.h:39-48 and :133 through the device helpers the capsule routines call."""
+    ps = server.PhysicsServerCUDA(0)
+    out = ps.test_segment_math(0, [[1, -1, 1, 1, 1, -1, -1, -2, -1, -1, 1, 1]])
+    assert np.allclose(out[0, 0:3], (1, -0.2, 0.2), atol=1e-5) and np.allclose(out[0, 3:6], (-1, -0.2, 0.2), atol=1e-5)   # is_equal_approx
+    # "Closest Distance Between Segments" == 2.0f exactly: the distance of the closest points
+    out = ps.test_segment_math(0, [[1, -2, 0, 1, 2, 0, -1, 2, 0, -1, -2, 0]])
+    assert float(np.linalg.norm(out[0, 0:3] - out[0, 3:6])) == 2.0
+    out = ps.test_segment_math(1, [[2, 1, 4, 1, 1, 1, 5, 5, 5]])
+    assert np.allclose(out[0], (2.33333, 2.33333, 2.33333), atol=1e-5)
+    # degenerate inputs: a point against a zero-length segment, parallel segments
+    out = ps.test_segment_math(1, [[3, 3, 3, 1, 1, 1, 1, 1, 1]])
+    assert np.array_equal(out[0], np.array([1, 1, 1], np.float32))
+    out = ps.test_segment_math(0, [[0, 0, 0, 1, 0, 0, 0, 1, 0, 1, 1, 0]])
+    assert np.all(np.isfinite(out)) and abs(float(np.linalg.norm(out[0, 0:3] - out[0, 3:6])) - 1.0) < 1e-6
+    ps.finish()
+
+
+def test_joint_parameters_limits_motors_and_priorities():
+    """Hinge limit (accumulated, clamped impulse) and motor, pin bias / damping / impulse clamp, extra sweeps for solver
+    priority 2: teacher-forced with the reference's sweep order, body state after the step within 1e-4 (measured: bit-equal)."""
+    _need_oracle()
+    sc = scenes.hanging_chains()
+    _, dump = parity.run_oracle(sc, 80)
+    # the limits do engage: without them a hinge with +-2 rad/s would leave [-0.35, 0.5] within the first second
+    w = parity.teacher_forced(sc, 80, [1, 5, 15, 30, 50, 79], dump=dump)
+    assert w["state"] < STATE_TOL, w
+    # and the parameters matter: the same scene with default joints departs from the reference
+    plain = scenes.hanging_chains()
+    plain.joints["flags"] &= scenes.JOINT_NO_COLLIDE
+    plain.joints["priority"] = 0
+    ps = parity.new_server(plain, dump)
+    parity.load_state(ps, dump, 30)
+    ps.set_solve_order(parity.solve_order(dump, 31))
+    ps.step(sc.dt)
+    av = ps.bodies_read(server.FIELD_ANGULAR_VELOCITY)
+    assert parity.rel_err(av, dump[("bodies", 31)][:, 15:18], 1.0) > 1e-2
+    ps.finish()
+
+
+def test_joint_parameters_can_change_and_joints_can_go_at_run_time():
+    _need_oracle()
+    sc = scenes.hanging_chains(3, 4)
+    plain = scenes.hanging_chains(3, 4)
+    plain.joints["flags"] &= scenes.JOINT_NO_COLLIDE
+    plain.joints["priority"] = 0
+    _, dump = parity.run_oracle(sc, 20)
+    ps = parity.new_server(plain, dump)
+    ps.joints_write(0, sc.joints)              # hinge_joint_set_param / set_flag / joint_set_solver_priority after creation
+    parity.load_state(ps, dump, 10)
+    ps.set_solve_order(parity.solve_order(dump, 11))
+    ps.step(sc.dt)
+    lv = ps.bodies_read(server.FIELD_LINEAR_VELOCITY)
+    assert parity.rel_err(lv, dump[("bodies", 11)][:, 12:15], 1.0) < STATE_TOL
+    # a destroyed joint stops acting: the lowest link of chain 0 falls freely
+    ps.set_solve_order(np.zeros((0, 3), np.int32))
+    last = 3                                    # joint 3 links bodies 3 and 4 of chain 0 (anchor = body 0)
+    ps.joints_destroy(last)
+    y0 = ps.bodies_read(server.FIELD_TRANSFORM)[4, 10]
+    for _ in range(30):
+        ps.step(sc.dt)
+    assert ps.bodies_read(server.FIELD_TRANSFORM)[4, 10] < y0 - 0.5
+    ps.finish()
+
+
+def test_axis_locks_and_damp_modes_in_free_flight():
+    """body_set_axis_lock (bradot_body_3d.cpp:685-699) and BODY_DAMP_MODE_REPLACE (:586-606): 40 free-running steps."""
+    _need_oracle()
+    sc = scenes.locks_and_damping(64)
+    _, dump = parity.run_oracle(sc, 40, dump_from=0, dump_every=10)
+    ps = parity.new_server(sc, dump)
+    for s in range(1, 41):
+        ps.step(sc.dt)
+        if s % 10 == 0:
+            ref = dump[("bodies", s)]
+            st = ps.bodies_read_state()
+            assert parity.rel_err(st[:, 0:12], ref[:, 0:12], 1.0) < STATE_TOL
+            assert parity.rel_err(st[:, 12:18], ref[:, 12:18], 1.0) < STATE_TOL
+    # the locks did something: a locked linear axis kept its velocity component at zero
+    locks = (sc.bodies["flags"] >> scenes.BODY_LOCK_SHIFT) & 63
+    lv = ps.bodies_read(server.FIELD_LINEAR_VELOCITY)
+    for ax in range(3):
+        sel = (locks & (1 << ax)) != 0
+        assert sel.any() and np.all(lv[sel, ax] == 0.0)
+    ps.finish()
+
+
+def test_axis_locks_and_damp_modes_with_contacts():
+    _need_oracle()
+    sc = scenes.locks_and_damping(48, on_plane=True)
+    w = parity.teacher_forced(sc, 60, [1, 15, 30, 45, 59])
+    assert w["colliding"] > 0 and w["contact"] < CONTACT_TOL and w["state"] < STATE_TOL, w
+
+
+def test_each_space_sweeps_its_own_number_of_iterations():
+    """SPACE_PARAM_SOLVER_ITERATIONS is per space (bradot_space_3d.h solver_iterations): 4 spaces with 4, 9, 14, 19 sweeps
+    in the same launches, sweep order imported space by space."""
+    _need_oracle()
+    sc = scenes.batched_worlds(4, lattice=(3, 3, 3))
+    sc.iterations, sc.iter_step = 4, 5
+    w = parity.teacher_forced(sc, 70, [30, 45, 55, 69])
+    assert w["colliding"] > 0 and w["contact"] < CONTACT_TOL and w["state"] < STATE_TOL, w
+    # the counts matter: with 19 sweeps everywhere space 0 ends a step with other velocities
+    _, dump = parity.run_oracle(sc, 56, dump_from=55)
+    same = scenes.batched_worlds(4, lattice=(3, 3, 3))
+    same.iterations = 19
+    ps = parity.new_server(same, dump)
+    parity.load_state(ps, dump, 55)
+    ps.set_solve_order(parity.solve_order(dump, 56))
+    ps.step(sc.dt)
+    lv = ps.bodies_read(server.FIELD_LINEAR_VELOCITY)
+    sp0 = sc.bodies["space"] == 0
+    assert parity.rel_err(lv[sp0], dump[("bodies", 56)][sp0, 12:15], 1.0) > 1e-4
+    ps.finish()
+
+
+def _apply_events(ps, events, step, freed):
+    for (s, body, kind, v) in events:
+        if s != step or body in freed:
+            continue
+        if kind == 0:
+            ps.body_set_state([body], server.BODY_STATE_TRANSFORM, v[:12])
+        elif kind == 1:
+            ps.body_set_state([body], server.BODY_STATE_LINEAR_VELOCITY, v[:3])
+        elif kind == 2:
+            ps.body_set_state([body], server.BODY_STATE_ANGULAR_VELOCITY, v[:3])
+        elif kind == 3:
+            ps.bodies_destroy([body])
+            freed.add(body)
+        elif kind == 4:
+            ps.body_set_state([body], server.BODY_STATE_SLEEPING, v[:1])
+        elif kind == 5:
+            ps.body_set_state([body], server.BODY_STATE_CAN_SLEEP, v[:1])
+
+
+def test_body_set_state_and_free_follow_the_reference():
+    """BradotBody3D::set_state (bradot_body_3d.cpp:352-417) and free(RID) (bradot_physics_server_3d.cpp:1572-1590) at run
+    time: a teleported sleeping body wakes, is orthonormalised and gets a new broadphase box; a moved static body wakes what
+    rests on it; velocities wake; SLEEPING clears velocities; CAN_SLEEP false wakes; freed bodies leave.  Free-running from
+    the same start, the active flag of every body equals the reference's after every step, positions agree to 2 mm."""
+    _need_oracle()
+    sc = scenes.scripted_events()
+    events = scenes.scripted_events_script()
+    steps = 160
+    _, dump = parity.run_oracle(sc, steps, events=events)
+    ps = parity.new_server(sc, dump)
+    freed = set()
+    for s in range(1, steps + 1):
+        _apply_events(ps, events, s, freed)
+        ps.step(sc.dt)
+        ref = dump[("bodies", s)]
+        st = ps.bodies_read_state()
+        alive = np.array([i not in freed for i in range(len(sc.bodies))])
+        assert np.array_equal(st[alive, 18], ref[alive, 18]), "active flags differ at step %d: %r vs %r" % (s, st[:, 18], ref[:, 18])
+        assert np.max(np.abs(st[alive, 9:12] - ref[alive, 9:12])) < 2e-3, "positions differ at step %d" % s
+        info = ps.stats()
+        assert info["collision_pairs"] == int(dump[("stats", s)][2]), "pair count differs at step %d" % s
+    # the script did what it says
+    assert dump[("bodies", 70)][3, 18] == 1 and dump[("bodies", 69)][3, 18] == 0        # teleport woke body 3
+    assert dump[("bodies", 80)][8, 18] == 1 and dump[("bodies", 79)][8, 18] == 0        # the moved platform woke its boxes
+    ps.finish()
+
+
+def test_freed_slots_are_reused_and_stay_consistent():
+    sc = scenes.scripted_events()
+    ps = parity.new_server(sc)
+    for _ in range(30):
+        ps.step(sc.dt)
+    n0 = ps.body_count()
+    ps.bodies_destroy([4, 6])
+    ps.step(sc.dt)
+    ids, _, _ = ps.pairs_read()
+    assert not np.isin(ids[:, :2], [4, 6]).any()                  # their pairs are gone with the next step
+    rec = sc.bodies[[4, 6]].copy()
+    rec["xf"][:, 10] = 3.0
+    slots = ps.bodies_create_slots(rec)
+    assert sorted(slots.tolist()) == [4, 6] and ps.body_count() == n0
+    extra = ps.bodies_create_slots(rec[:1])
+    assert extra[0] == n0 and ps.body_count() == n0 + 1          # no free slot left: appended
+    for _ in range(90):
+        ps.step(sc.dt)
+    y = ps.bodies_read(server.FIELD_TRANSFORM)[:, 10]
+    assert abs(y[4] - 0.25) < 0.02 and abs(y[6] - 0.25) < 0.02   # fell and came to rest on the ground
+    ps.finish()
+
+
+def test_inactive_space_is_not_stepped_and_resumes_unchanged():
+    sc = scenes.batched_worlds(3, lattice=(3, 3, 3))
+    ps = parity.new_server(sc)
+    twin = parity.new_server(sc)
+    for _ in range(50):
+        ps.step(sc.dt)
+        twin.step(sc.dt)
+    ps.space_set_active(1, False)
+    frozen = ps.bodies_read_state()
+    sp1 = sc.bodies["space"] == 1
+    for _ in range(20):
+        ps.step(sc.dt)
+    now = ps.bodies_read_state()
+    assert np.array_equal(now[sp1], frozen[sp1])                  # space 1 did not move
+    assert not np.array_equal(now[~sp1], frozen[~sp1])            # the others did
+    assert ps.stats()["active_objects"] <= int((~sp1 & (sc.bodies["mode"] >= 2)).sum())
+    ps.space_set_active(1, True)
+    for _ in range(20):
+        ps.step(sc.dt)
+        twin.step(sc.dt)
+    # space 1 took its 20 steps later than its twin, from the same state with the same cached contacts
+    a = ps.bodies_read_state()[sp1]
+    b = twin.bodies_read_state()[sp1]
+    assert np.allclose(a[:, 9:12], b[:, 9:12], atol=2e-3)         # (the sweep order depends on the other spaces' pair counts)
+    ps.finish()
+    twin.finish()
+
+
+def test_body_update_after_upload_changes_mode_layers_and_parameters():
+    sc = scenes.scripted_events()
+    ps = parity.new_server(sc)
+    for _ in range(40):
+        ps.step(sc.dt)
+    # body_set_mode(STATIC) on a resting box, body_set_collision_mask(0) on another: it falls through the ground
+    rec = sc.bodies[[2, 3]].copy()
+    rec["mode"][0] = scenes.MODE_STATIC
+    rec["mask"][1] = 0
+    rec["layer"][1] = 0
+    ps.bodies_update([2, 3], rec)
+    ps.body_set_state([3], server.BODY_STATE_SLEEPING, [0.0])
+    y3 = ps.bodies_read(server.FIELD_TRANSFORM)[3, 10]
+    for _ in range(30):
+        ps.step(sc.dt)
+    st = ps.bodies_read_state()
+    assert st[2, 18] == 0 and abs(st[2, 10] - 0.25) < 0.02
+    assert st[3, 10] < y3 - 0.5
+    # body_set_param(MASS) keeps the body where it is and changes its inverse mass
+    rec = sc.bodies[[5]].copy()
+    rec["mass"] = 4.0
+    ps.bodies_update([5], rec)
+    mp = ps.bodies_read(server.FIELD_MASS_PROPS, 5, 1)
+    assert abs(mp[0, 0] - 0.25) < 1e-7
+    ps.finish()
