@@ -22,16 +22,17 @@ def _stale(obj, src):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(verbose=False, force=False):
+def build(verbose=False, force=False, lib=LIB, defines=()):
+    """`lib` / `defines`: A/B builds of the same ABI next to the default one (BPC_LIBRARY selects one at run time)."""
     nvcc = os.environ.get("NVCC", "nvcc")
     objs = []
     procs = []
     for s in SOURCES:
         src = os.path.join(CSRC, s)
-        obj = os.path.join(CSRC, s.replace(".cu", ".o"))
+        obj = os.path.join(CSRC, s.replace(".cu", ".o" if lib == LIB else "." + os.path.basename(lib) + ".o"))
         objs.append(obj)
         if force or _stale(obj, src):
-            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+            cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
             procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for s, p in procs:
@@ -43,9 +44,9 @@ def build(verbose=False, force=False):
             print(out)
     if failed:
         raise RuntimeError("CUDA build failed")
-    if procs or not os.path.exists(LIB):
-        subprocess.run([nvcc, "-shared", "-o", LIB] + objs + ["-lcudart"], check=True)
-    return LIB
+    if procs or not os.path.exists(lib):
+        subprocess.run([nvcc, "-shared", "-o", lib] + objs + ["-lcudart"], check=True)
+    return lib
 
 
 if __name__ == "__main__":

@@ -5,6 +5,7 @@
 // (modules/bradot_physics_3d/bradot_body_3d.cpp:56-166).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/bradot_physics_cuda.h"
@@ -32,6 +33,9 @@ extern "C" bpc_context *bpc_create(int device) {
         return nullptr;
     }
     memset(ctx->h_counters, 0, CNT_N * sizeof(uint32_t));
+    // A/B switch for measurements: BPC_NO_BINS=1 keeps every constraint on the grid-barrier path of the solver
+    const char *nb = getenv("BPC_NO_BINS");
+    ctx->use_bins = !(nb && nb[0] == '1');
     return ctx;
 }
 
@@ -50,7 +54,7 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
         ctx->pair_keys[b].free_(); ctx->pair_hdr[b].free_(); ctx->cgeo[b].free_(); ctx->cacc[b].free_();
     }
     ctx->except_keys.free_(); ctx->con_list.free_(); ctx->con_color.free_(); ctx->con_sorted.free_(); ctx->con_sorted_alt.free_();
-    ctx->con_info.free_(); ctx->body_best.free_(); ctx->body_colmask.free_(); ctx->color_start.free_(); ctx->scontacts.free_();
+    ctx->con_info.free_(); ctx->con_bin.free_(); ctx->con_sorted_color.free_(); ctx->con_cls.free_(); ctx->bin_tab.free_(); ctx->bin_base.free_(); ctx->body_best.free_(); ctx->body_colmask.free_(); ctx->color_start.free_(); ctx->scontacts.free_();
     ctx->forced_order.free_(); ctx->forced_level_start.free_(); ctx->forced_keys.free_(); ctx->d_joints.free_();
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     delete ctx;

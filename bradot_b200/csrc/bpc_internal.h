@@ -104,6 +104,15 @@ struct SpaceParams {
     int alive = 1;  // 0 after bpc_space_destroy
 };
 
+// Solver bins: islands whose root index shares a block of BIN_BLOCK body indices; one small CTA sweeps a bin whose dynamic bodies
+// span fewer than BIN_MAX_BODIES indices (their velocity records sit in shared memory) and that has at most BIN_MAX_CONS
+// constraints.
+#ifndef BIN_BLOCK
+#define BIN_BLOCK 256u
+#define BIN_MAX_BODIES 704u
+#define BIN_MAX_CONS 2048u
+#endif
+
 // stages timed by bpc_set_profiling: forces, broadphase, islands, narrowphase, schedule, solve, integrate+sleep
 #define BPC_N_STAGES 7
 
@@ -250,6 +259,13 @@ struct bpc_context {
     DevBuf<uint64_t> body_best;
     DevBuf<uint64_t> body_colmask;
     DevBuf<uint32_t> color_start; // 66 entries + count
+    // solver bins (k_graph.cu): bin of every constraint; per-bin count / lowest body / highest body / fits-one-CTA;
+    // per (bin, colour) histogram, offsets and scatter cursors
+    DevBuf<uint32_t> con_bin, bin_tab, bin_base;
+    DevBuf<uint16_t> con_sorted_color; // colour * 4 + work class of each entry of con_sorted
+    DevBuf<uint8_t> con_cls;           // work class (cached contacts - 1) of each entry of con_list
+    uint32_t n_bins = 0;
+    bool use_bins = true;
     DevBuf<SolveContact> scontacts;
     DevBuf<uint32_t> forced_order; // teacher-forced sweep order (pair indices), optional
     DevBuf<uint32_t> forced_level_start;
@@ -264,7 +280,7 @@ struct bpc_context {
 };
 
 enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIVE = 4, CNT_ISLANDS = 5, CNT_CONTACTS = 6,
-       CNT_OVERFLOW = 7, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_ROUND = 20 /* 3 slots */, CNT_N = 32 };
+       CNT_OVERFLOW = 7, CNT_GROUPS = 8 /* colours on the grid-barrier path */, CNT_BARRIER_CONS = 9, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_ROUND = 20 /* 3 slots */, CNT_N = 32 };
 
 #define BPC_CHECK(x)                                                                                  \
     do {                                                                                              \

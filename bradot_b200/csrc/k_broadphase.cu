@@ -313,10 +313,11 @@ __global__ void __launch_bounds__(BP_THREADS) k_match(uint32_t n_new, const uint
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n_new) return;
     uint64_t key = knew[k];
-    // pair counts only steer the margin of items that move; a world boundary pairs with every body of
-    // its space, and counting those on one address would serialise the kernel
-    if ((meta[(uint32_t)(key >> 32)].x & 0xffu) != MODE_STATIC) atomicAdd(&npairs[(uint32_t)(key >> 32)], 1u);
-    if ((meta[(uint32_t)key].x & 0xffu) != MODE_STATIC) atomicAdd(&npairs[(uint32_t)key], 1u);
+    // pair counts steer the margin of an item's next move (static bodies can be moved too: body_set_state); a world
+    // boundary pairs with every body of its space, counting those on one address would serialise the kernel, and its
+    // unbounded box needs no margin
+    if ((meta[(uint32_t)(key >> 32)].x >> 24) != SH_PLANE) atomicAdd(&npairs[(uint32_t)(key >> 32)], 1u);
+    if ((meta[(uint32_t)key].x >> 24) != SH_PLANE) atomicAdd(&npairs[(uint32_t)key], 1u);
     uint32_t A = (uint32_t)(key >> 32);
     uint32_t lo = a_begin[A], hi = a_end[A], end = hi; // empty run: begin = end = 0
     while (lo < hi) {

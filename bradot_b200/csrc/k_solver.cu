@@ -14,6 +14,8 @@
 namespace cg = cooperative_groups;
 
 #define SV_THREADS 128
+#define BIN_COLS_SV 65 // colours 0..63 + the overflow group, as laid out by k_graph.cu (BIN_COLS)
+#define BIN_KEYS_SV (BIN_COLS_SV * 4) // (colour, work class) runs
 // MIN_VELOCITY 0.0001 and CMP_EPSILON 0.00001 are doubles in the reference (bradot_body_pair_3d.cpp:39, math_defs.h:35) and
 // the floats are promoted for the compare.  float(0.0001) < 0.0001 < nextafter(float(0.0001)), so for a float x
 // "(double)x > 0.0001" is exactly "x > 0.0001f" (same for 0.00001): the compares stay in fp32, bit-identical.
@@ -33,7 +35,8 @@ struct SvArgs {
     const SpaceParams *spaces;
     const uint4 *meta;
     const uint32_t *sched;       // constraint ids in sweep order
-    const uint32_t *group_start; // n_groups + 1 offsets into sched
+    const uint32_t *group_start; // offsets into sched: group g = [group_start[g * group_stride], group_start[(g + 1) * group_stride])
+    uint32_t group_stride;       // 1, or 4 when every colour is laid out as four runs by work class
     const uint32_t *n_groups;    // device scalar
     uint32_t serial_group;       // index of a group that must run on one thread (colour overflow), or 0xffffffff
     uint4 *info;
@@ -42,6 +45,9 @@ struct SvArgs {
     const JointRec *joints;
     JointSetup *jsetup; // the solver keeps a hinge's accumulated limit impulse in it
     uint32_t max_priority;
+    // solver bins (k_solve_bins): per bin "fits one CTA", lowest / highest body, offsets of its colour runs
+    const uint32_t *bin_ok, *bin_lo, *bin_hi, *bin_base;
+    const uint16_t *sched_color; // colour * 4 + work class of each entry of `sched`
     // continuous collision detection only
     const BodyXf *shape_xf;
     const float4 *shape_p;
@@ -59,25 +65,69 @@ struct BodyS { // the part of a body the solver touches
     float inv_mass;
 };
 
-__device__ __forceinline__ void load_body(const SvArgs &a, uint32_t i, bool collides, BodyS &b, float &friction, float &bounce) {
-    BodyVel v = a.vel[i];
-    BodyMassW m = a.massw[i];
-    b.lin = f4v(v.lin); b.ang = f4v(v.ang); b.blin = f4v(v.blin); b.bang = f4v(v.bang);
-    b.com = V3(m.i0.w, m.i1.w, m.i2.w);
-    friction = m.m.y;
-    bounce = m.m.z;
+// Bodies of a solver bin (k_solve_bins): the velocity records (lin, ang, bias lin, bias ang = 12 floats) of the body indices
+// [lo, lo + n) in shared memory, SB_STRIDE floats apart (odd, so consecutive bodies fall into different banks).  The mass data
+// is read-only during the solve and comes through the read-only cache.
+#ifndef SB_MASS_IN_SHARED
+#define SB_MASS_IN_SHARED 0
+#endif
+#if SB_MASS_IN_SHARED
+#define SB_STRIDE 25
+#else
+#define SB_STRIDE 13
+#endif
+struct ShBodies {
+    float *rec;
+    uint8_t *touched; // body written by a constraint of this bin: only those go back to global memory
+    uint32_t lo;
+};
+
+// SH: a body the constraint may write (`collides`) has its velocities in the bin's shared-memory copy; bodies it only
+// reads (static, kinematic) come from global memory either way -- nobody writes those during the solve.
+// ROLE: which half of the velocity record is needed -- 1 = the bias ("split impulse") velocities, 2 = the real ones, 0 = both.
+template <bool SH, int ROLE>
+__device__ __forceinline__ void load_body(const SvArgs &a, const ShBodies &sb, uint32_t i, bool collides, BodyS &b, float &friction) {
+    float4 i0, i1, i2, mm;
+    if (SH && collides) {
+        const float *r = sb.rec + (size_t)(i - sb.lo) * SB_STRIDE;
+        if (ROLE != 1) { b.lin = V3(r[0], r[1], r[2]); b.ang = V3(r[3], r[4], r[5]); }
+        if (ROLE != 2) { b.blin = V3(r[6], r[7], r[8]); b.bang = V3(r[9], r[10], r[11]); }
+#if SB_MASS_IN_SHARED
+        b.iinv = M3(V3(r[12], r[13], r[14]), V3(r[15], r[16], r[17]), V3(r[18], r[19], r[20]));
+        b.com = V3(r[21], r[22], r[23]);
+        b.inv_mass = r[24];
+        friction = __ldg(&a.massw[i].m).y;
+        return;
+#endif
+    } else {
+        const float4 *vp = (const float4 *)(a.vel + i);
+        if (ROLE != 1) { b.lin = f4v(vp[0]); b.ang = f4v(vp[1]); }
+        if (ROLE != 2) { b.blin = f4v(vp[2]); b.bang = f4v(vp[3]); }
+    }
+    const float4 *mp = (const float4 *)(a.massw + i); // read-only during the solve
+    i0 = __ldg(mp); i1 = __ldg(mp + 1); i2 = __ldg(mp + 2); mm = __ldg(mp + 3);
+    b.com = V3(i0.w, i1.w, i2.w);
+    friction = mm.y;
     if (collides) {
-        b.iinv = M3(f4v(m.i0), f4v(m.i1), f4v(m.i2));
-        b.inv_mass = m.m.x;
+        b.iinv = M3(f4v(i0), f4v(i1), f4v(i2));
+        b.inv_mass = mm.x;
     } else {
         b.iinv = m3_zero();
         b.inv_mass = 0.f;
     }
 }
-__device__ __forceinline__ void store_body(const SvArgs &a, uint32_t i, const BodyS &b) {
-    BodyVel v;
-    v.lin = v4(b.lin, 0.f); v.ang = v4(b.ang, 0.f); v.blin = v4(b.blin, 0.f); v.bang = v4(b.bang, 0.f);
-    a.vel[i] = v;
+template <bool SH, int ROLE>
+__device__ __forceinline__ void store_body(const SvArgs &a, const ShBodies &sb, uint32_t i, const BodyS &b) {
+    if (SH) {
+        float *r = sb.rec + (size_t)(i - sb.lo) * SB_STRIDE;
+        if (ROLE != 1) { r[0] = b.lin.x; r[1] = b.lin.y; r[2] = b.lin.z; r[3] = b.ang.x; r[4] = b.ang.y; r[5] = b.ang.z; }
+        if (ROLE != 2) { r[6] = b.blin.x; r[7] = b.blin.y; r[8] = b.blin.z; r[9] = b.bang.x; r[10] = b.bang.y; r[11] = b.bang.z; }
+        sb.touched[i - sb.lo] = 1;
+        return;
+    }
+    float4 *vp = (float4 *)(a.vel + i);
+    if (ROLE != 1) { vp[0] = v4(b.lin, 0.f); vp[1] = v4(b.ang, 0.f); }
+    if (ROLE != 2) { vp[2] = v4(b.blin, 0.f); vp[3] = v4(b.bang, 0.f); }
 }
 __device__ __forceinline__ void apply_impulse(BodyS &b, V3 j, V3 pos) {
     b.lin += j * b.inv_mass;
@@ -177,8 +227,8 @@ __device__ __noinline__ void ccd_pair(const SvArgs &a, uint32_t ia, uint32_t ib,
 }
 
 // pre_solve of one pair; writes SolveContact records at slot s and warm-starts the bodies
-template <bool CCD>
-__device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
+template <bool CCD, bool SH>
+__device__ inline void pre_solve_pair(const SvArgs &a, const ShBodies &sb, uint32_t s, uint32_t k) {
     uint64_t key = a.keys[k];
     uint32_t ia = (uint32_t)(key >> 32), ib = (uint32_t)key;
     uint32_t bits = __float_as_uint(a.hdr[k].sep.w);
@@ -193,9 +243,10 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
     // each space sweeps its own number of times (SPACE_PARAM_SOLVER_ITERATIONS); a body pair has solver priority 1
     const uint32_t sweeps = ((uint32_t)space.iterations << 24) | (1u << 20);
     BodyS A, B;
-    float fA, fB, boA, boB;
-    load_body(a, ia, cA, A, fA, boA);
-    load_body(a, ib, cB, B, fB, boB);
+    float fA, fB;
+    load_body<SH, 0>(a, sb, ia, cA, A, fA);
+    load_body<SH, 0>(a, sb, ib, cB, B, fB);
+    const float boA = a.massw[ia].m.z, boB = a.massw[ib].m.z;
     BodyXf xa = a.xf[ia], xb = a.xf[ib];
     M3 bA(f4v(xa.r0), f4v(xa.r1), f4v(xa.r2)), bB(f4v(xb.r0), f4v(xb.r1), f4v(xb.r2));
     V3 offset_B = f4v(xb.o) - f4v(xa.o);
@@ -254,15 +305,20 @@ __device__ inline void pre_solve_pair(const SvArgs &a, uint32_t s, uint32_t k) {
         n_active++;
     }
     if (any) {
-        if (cA) store_body(a, ia, A);
-        if (cB) store_body(a, ib, B);
+        if (cA) store_body<SH, 2>(a, sb, ia, A); // the warm start moves the real velocities only
+        if (cB) store_body<SH, 2>(a, sb, ib, B);
         atomicAdd(&a.counters[CNT_ACTIVE_CONTACTS], (uint32_t)n_active);
     }
     a.info[s] = make_uint4(ia, ib, (uint32_t)count | (cA ? 0x200u : 0u) | (cB ? 0x400u : 0u) | (any ? 0x800u : 0u) | sweeps, k);
 }
 
-// `it` = sweep number, `round` = priority round (1 = the regular sweeps, bradot_step_3d.cpp:134-160)
-__device__ inline void solve_pair(const SvArgs &a, uint32_t s, int it, uint32_t round) {
+// One sweep over the contacts of a pair: BradotBodyPair3D::solve (bradot_body_pair_3d.cpp:457-599).  `it` = sweep number,
+// `round` = priority round (1 = the regular sweeps, bradot_step_3d.cpp:134-160).
+// (Measured and dropped: two threads per pair, one for the split-impulse block on the bias velocities and one for the
+// normal + friction blocks on the real ones -- independent data flows -- with per-role activity words.  Every role pays the
+// dependent-load chain info -> bodies -> contact again: sweeps 15-30 % slower on C2 and C5.)
+template <bool SH>
+__device__ inline void solve_pair(const SvArgs &a, const ShBodies &sb, uint32_t s, int it, uint32_t round) {
     uint4 inf = a.info[s];
     // first contact record requested together with the info word: its latency overlaps the body gathers
     SolveContact first = a.sc[s];
@@ -271,9 +327,9 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s, int it, uint32_t 
     int count = inf.z & 0xffu;
     bool cA = inf.z & 0x200u, cB = inf.z & 0x400u;
     BodyS A, B;
-    float f0, f1, f2, f3;
-    load_body(a, ia, cA, A, f0, f1);
-    load_body(a, ib, cB, B, f2, f3);
+    float fA, fB;
+    load_body<SH, 0>(a, sb, ia, cA, A, fA);
+    load_body<SH, 0>(a, sb, ib, cB, B, fB);
     bool touched = false;
     for (int c = 0; c < count; c++) {
         SolveContact sc = c == 0 ? first : a.sc[(size_t)c * a.sc_stride + s];
@@ -350,8 +406,8 @@ __device__ inline void solve_pair(const SvArgs &a, uint32_t s, int it, uint32_t 
         touched = true;
     }
     if (touched) {
-        if (cA) store_body(a, ia, A);
-        if (cB) store_body(a, ib, B);
+        if (cA) store_body<SH, 0>(a, sb, ia, A);
+        if (cB) store_body<SH, 0>(a, sb, ib, B);
     }
 }
 
@@ -494,8 +550,16 @@ __global__ void __launch_bounds__(128) k_joint_setup(JsArgs a) {
 __device__ __forceinline__ float ang_denominator(const BodyS &b, V3 axis) { // compute_angular_impulse_denominator
     return dot(axis, xform_inv(b.iinv, axis));
 }
+// a static or kinematic body in a joint keeps its real inverse mass / inertia in the reference's formulas (both are zero
+// for a static body, and a kinematic one's inverse inertia tensor is zero as well): load them as they are stored
+__device__ __forceinline__ void load_joint_static(const SvArgs &a, uint32_t i, BodyS &b) {
+    BodyMassW m = a.massw[i];
+    b.iinv = M3(f4v(m.i0), f4v(m.i1), f4v(m.i2));
+    b.inv_mass = m.m.x;
+}
 
-__device__ inline void solve_joint(const SvArgs &a, uint32_t s, int it, uint32_t round) {
+template <bool SH>
+__device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t s, int it, uint32_t round) {
     uint4 inf = a.info[s];
     if (it >= (int)(inf.z >> 24) || round > ((inf.z >> 20) & 15u)) return;
     const JointSetup js = a.jsetup[inf.w];
@@ -503,10 +567,13 @@ __device__ inline void solve_joint(const SvArgs &a, uint32_t s, int it, uint32_t
     if (!(flags & 4u)) return;
     bool dynA = flags & 1u, dynB = flags & 2u;
     if (!dynA && !dynB) return;
+    // a joint reads the true mass data of both bodies; only a dynamic one (the ones a bin holds) is ever written
     BodyS A, B;
-    float f0, f1, f2, f3;
-    load_body(a, inf.x, true, A, f0, f1);
-    load_body(a, inf.y, true, B, f2, f3);
+    float f0, f1;
+    load_body<SH, 2>(a, sb, inf.x, dynA, A, f0);
+    load_body<SH, 2>(a, sb, inf.y, dynB, B, f1);
+    if (!dynA) load_joint_static(a, inf.x, A);
+    if (!dynB) load_joint_static(a, inf.y, B);
     V3 pA = f4v(js.pa), pB = f4v(js.pb), dpos = f4v(js.dpos);
     const float4 rows[3] = { js.n0, js.n1, js.n2 };
     uint32_t type = (inf.z >> 16) & 15u;
@@ -592,8 +659,8 @@ __device__ inline void solve_joint(const SvArgs &a, uint32_t s, int it, uint32_t
             if (dynB) B.ang += xform(B.iinv, -motorImp - V3(0.f, 0.f, 0.f));
         }
     }
-    if (dynA) store_body(a, inf.x, A);
-    if (dynB) store_body(a, inf.y, B);
+    if (dynA) store_body<SH, 2>(a, sb, inf.x, A); // joints act on the real velocities only
+    if (dynB) store_body<SH, 2>(a, sb, inf.y, B);
 }
 
 __device__ inline void pre_solve_joint(const SvArgs &a, uint32_t s, uint32_t j) {
@@ -617,59 +684,196 @@ __device__ inline void finish_pair(const SvArgs &a, uint32_t s) {
 
 // CCD = some body of the scene has continuous collision detection: only that variant carries the tunnelling test (its code
 // costs the common variant 13 % when it merely sits in the kernel)
+// The grid-barrier path in two cooperative launches: k_presolve (effective masses, bias, restitution, warm start: group by
+// group, since the warm start writes body velocities) and k_sweeps (the Gauss-Seidel sweeps + write-back of the accumulated
+// impulses).  Two kernels so that the sweeps are not compiled to the register budget of the pre-solve.
 template <bool CCD>
-__global__ void __launch_bounds__(SV_THREADS) k_solve(SvArgs a) {
+__global__ void __launch_bounds__(SV_THREADS) k_presolve(SvArgs a) {
     cg::grid_group grid = cg::this_grid();
     uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     uint32_t ng = *a.n_groups;
-    // phase 0: pre-solve, group by group (warm start writes body velocities)
+    const ShBodies none = { nullptr, nullptr, 0u };
     for (uint32_t g = 0; g < ng; g++) {
-        uint32_t lo = a.group_start[g], hi = a.group_start[g + 1];
+        uint32_t lo = a.group_start[g * a.group_stride], hi = a.group_start[(g + 1) * a.group_stride];
         if (g == a.serial_group) {
             if (tid == 0) {
                 for (uint32_t s = lo; s < hi; s++) {
                     uint32_t id = a.sched[s];
-                    if (id < a.n_pairs) pre_solve_pair<CCD>(a, s, id);
+                    if (id < a.n_pairs) pre_solve_pair<CCD, false>(a, none, s, id);
                     else if (id != 0xffffffffu) pre_solve_joint(a, s, id - a.n_pairs);
                 }
             }
         } else {
             for (uint32_t s = lo + tid; s < hi; s += nth) {
                 uint32_t id = a.sched[s];
-                if (id < a.n_pairs) pre_solve_pair<CCD>(a, s, id);
+                if (id < a.n_pairs) pre_solve_pair<CCD, false>(a, none, s, id);
                 else if (id != 0xffffffffu) pre_solve_joint(a, s, id - a.n_pairs);
             }
         }
         grid.sync();
     }
+}
+
+#ifndef SV_MIN_BLOCKS
+#define SV_MIN_BLOCKS 3
+#endif
+__global__ void __launch_bounds__(SV_THREADS, SV_MIN_BLOCKS) k_sweeps(SvArgs a) {
+    cg::grid_group grid = cg::this_grid();
+    uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    uint32_t ng = *a.n_groups;
+    const ShBodies none = { nullptr, nullptr, 0u };
     // `iterations` sweeps over everything, then again for the constraints of solver priority >= 2, >= 3, ...
     // (bradot_step_3d.cpp:134-160); a constraint sits out the sweeps beyond its own space's iteration count
     for (uint32_t round = 1; round <= a.max_priority; round++) {
         for (int it = 0; it < a.iterations; it++) {
             for (uint32_t g = 0; g < ng; g++) {
-                uint32_t lo = a.group_start[g], hi = a.group_start[g + 1];
+                uint32_t lo = a.group_start[g * a.group_stride], hi = a.group_start[(g + 1) * a.group_stride];
                 if (g == a.serial_group) {
                     if (tid == 0) {
                         for (uint32_t s = lo; s < hi; s++) {
                             uint32_t id = a.sched[s];
-                            if (id < a.n_pairs) solve_pair(a, s, it, round);
-                            else if (id != 0xffffffffu) solve_joint(a, s, it, round);
+                            if (id < a.n_pairs) solve_pair<false>(a, none, s, it, round);
+                            else if (id != 0xffffffffu) solve_joint<false>(a, none, s, it, round);
                         }
                     }
                 } else {
                     for (uint32_t s = lo + tid; s < hi; s += nth) {
                         uint32_t id = a.sched[s];
-                        if (id < a.n_pairs) solve_pair(a, s, it, round);
-                        else if (id != 0xffffffffu) solve_joint(a, s, it, round);
+                        if (id < a.n_pairs) solve_pair<false>(a, none, s, it, round);
+                        else if (id != 0xffffffffu) solve_joint<false>(a, none, s, it, round);
                     }
                 }
                 grid.sync();
             }
         }
     }
-    uint32_t total = a.group_start[ng];
+    uint32_t total = a.group_start[ng * a.group_stride];
     for (uint32_t s = tid; s < total; s += nth) {
         if (a.sched[s] < a.n_pairs) finish_pair(a, s);
+    }
+}
+
+// One small CTA (SB_THREADS threads) per solver bin (k_graph.cu): the islands of a bin touch no body outside it, so the whole solve -- pre-solve,
+// every sweep of every priority round, write-back of the accumulated impulses -- runs here with __syncwarp() between the
+// colour groups and the bin's body velocities in shared memory.  Same colours, same order inside an island as on the
+// grid-barrier path, hence the same arithmetic.  The point is not bandwidth but stalls: on the barrier path a sweep is
+// ~30 grid-wide phases, each as long as its slowest constraint (ncu: 86 % of cycles without an eligible warp); here every
+// resident warp always has its own next group to run.
+#ifndef SB_THREADS
+#define SB_THREADS 64
+#endif
+#if SB_THREADS == 32
+#define SB_SYNC() __syncwarp()
+#else
+#define SB_SYNC() __syncthreads()
+#endif
+__global__ void __launch_bounds__(SB_THREADS) k_solve_bins(SvArgs a) {
+    extern __shared__ float4 sb_mem[];
+    const uint32_t bin = blockIdx.x;
+    if (!a.bin_ok[bin]) return;
+    const uint32_t lane = threadIdx.x; // index in the CTA
+    const uint32_t seg_lo = a.bin_base[BIN_KEYS_SV + bin], seg_n = a.bin_base[BIN_KEYS_SV + bin + 1] - seg_lo;
+    const uint32_t body_lo = a.bin_lo[bin], nb = a.bin_hi[bin] - body_lo + 1;
+    ShBodies sb;
+    sb.rec = (float *)sb_mem;
+    sb.touched = (uint8_t *)(sb.rec + (size_t)BIN_MAX_BODIES * SB_STRIDE);
+    sb.lo = body_lo;
+    uint16_t *order = (uint16_t *)(sb.touched + BIN_MAX_BODIES); // the segment's entries ordered by (colour, work class)
+    uint32_t *cstart = (uint32_t *)(order + BIN_MAX_CONS);       // [BIN_KEYS_SV + 1] offsets into `order`
+    uint32_t *groups = cstart + BIN_KEYS_SV + 1;                 // the colours in use, their number in the last slot
+    for (uint32_t j = lane; j < nb; j += SB_THREADS) {
+        BodyVel v = a.vel[body_lo + j];
+        float *r = sb.rec + (size_t)j * SB_STRIDE;
+        r[0] = v.lin.x; r[1] = v.lin.y; r[2] = v.lin.z; r[3] = v.ang.x; r[4] = v.ang.y; r[5] = v.ang.z;
+        r[6] = v.blin.x; r[7] = v.blin.y; r[8] = v.blin.z; r[9] = v.bang.x; r[10] = v.bang.y; r[11] = v.bang.z;
+#if SB_MASS_IN_SHARED
+        BodyMassW m = a.massw[body_lo + j];
+        r[12] = m.i0.x; r[13] = m.i0.y; r[14] = m.i0.z; r[15] = m.i1.x; r[16] = m.i1.y; r[17] = m.i1.z;
+        r[18] = m.i2.x; r[19] = m.i2.y; r[20] = m.i2.z; r[21] = m.i0.w; r[22] = m.i1.w; r[23] = m.i2.w;
+        r[24] = m.m.x;
+#endif
+        sb.touched[j] = 0;
+    }
+    // counting sort of the segment by (colour, work class)
+    for (uint32_t c = lane; c <= BIN_KEYS_SV; c += SB_THREADS) cstart[c] = 0;
+    SB_SYNC();
+    for (uint32_t k = lane; k < seg_n; k += SB_THREADS) atomicAdd(&cstart[a.sched_color[seg_lo + k] + 1], 1u);
+    SB_SYNC();
+    if (lane == 0) {
+        uint32_t run = 0, ng = 0;
+        for (uint32_t c = 0; c < BIN_KEYS_SV; c++) {
+            uint32_t cnt = cstart[c + 1];
+            if (cnt && (ng == 0 || groups[ng - 1] != c / 4)) groups[ng++] = c / 4;
+            cstart[c] = run; // the start of run c: used as the scatter cursor below, shifted back afterwards
+            run += cnt;
+        }
+        cstart[BIN_KEYS_SV] = run;
+        groups[BIN_COLS_SV] = ng;
+    }
+    SB_SYNC();
+    for (uint32_t k = lane; k < seg_n; k += SB_THREADS) {
+        uint32_t c = a.sched_color[seg_lo + k];
+        order[atomicAdd(&cstart[c], 1u)] = (uint16_t)k;
+    }
+    SB_SYNC();
+    if (lane == 0) { // every cursor ended at the next run's start
+        for (int c = BIN_KEYS_SV; c > 0; c--) cstart[c] = cstart[c - 1];
+        cstart[0] = 0;
+    }
+    SB_SYNC();
+    const uint32_t ng = groups[BIN_COLS_SV];
+    for (uint32_t gi = 0; gi < ng; gi++) {
+        uint32_t g = groups[gi], lo = cstart[g * 4], hi = cstart[g * 4 + 4];
+        if (g == a.serial_group) {
+            if (lane == 0) {
+                for (uint32_t q = lo; q < hi; q++) {
+                    uint32_t s = seg_lo + order[q], id = a.sched[s];
+                    if (id < a.n_pairs) pre_solve_pair<false, true>(a, sb, s, id);
+                    else pre_solve_joint(a, s, id - a.n_pairs);
+                }
+            }
+        } else {
+            for (uint32_t q = lo + lane; q < hi; q += SB_THREADS) {
+                uint32_t s = seg_lo + order[q], id = a.sched[s];
+                if (id < a.n_pairs) pre_solve_pair<false, true>(a, sb, s, id);
+                else pre_solve_joint(a, s, id - a.n_pairs);
+            }
+        }
+        SB_SYNC();
+    }
+    for (uint32_t round = 1; round <= a.max_priority; round++) {
+        for (int it = 0; it < a.iterations; it++) {
+            for (uint32_t gi = 0; gi < ng; gi++) {
+                uint32_t g = groups[gi], lo = cstart[g * 4], hi = cstart[g * 4 + 4];
+                if (g == a.serial_group) {
+                    if (lane == 0) {
+                        for (uint32_t q = lo; q < hi; q++) {
+                            uint32_t s = seg_lo + order[q];
+                            if (a.sched[s] < a.n_pairs) solve_pair<true>(a, sb, s, it, round);
+                            else solve_joint<true>(a, sb, s, it, round);
+                        }
+                    }
+                } else {
+                    for (uint32_t q = lo + lane; q < hi; q += SB_THREADS) {
+                        uint32_t s = seg_lo + order[q];
+                        if (a.sched[s] < a.n_pairs) solve_pair<true>(a, sb, s, it, round);
+                        else solve_joint<true>(a, sb, s, it, round);
+                    }
+                }
+                SB_SYNC();
+            }
+        }
+    }
+    for (uint32_t k = lane; k < seg_n; k += SB_THREADS) {
+        if (a.sched[seg_lo + k] < a.n_pairs) finish_pair(a, seg_lo + k);
+    }
+    for (uint32_t j = lane; j < nb; j += SB_THREADS) {
+        if (!sb.touched[j]) continue;
+        const float *r = sb.rec + (size_t)j * SB_STRIDE;
+        BodyVel v;
+        v.lin = make_float4(r[0], r[1], r[2], 0.f); v.ang = make_float4(r[3], r[4], r[5], 0.f);
+        v.blin = make_float4(r[6], r[7], r[8], 0.f); v.bang = make_float4(r[9], r[10], r[11], 0.f);
+        a.vel[body_lo + j] = v;
     }
 }
 
@@ -724,12 +928,20 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
         a.sched = ctx->forced_order.p;
         a.group_start = ctx->forced_level_start.p;
         a.n_groups = ctx->forced_level_start.p + ctx->n_forced_levels + 1;
+        a.group_stride = 1;
         a.serial_group = 0xffffffffu;
-    } else {
+    } else { // bin 0 of the sorted list = the grid-barrier path; its colour runs start the offset table
+        uint32_t n_keys = BIN_KEYS_SV + ctx->n_bodies / BIN_BLOCK + 1;
+        a.group_stride = 4;
         a.sched = ctx->con_sorted.p;
-        a.group_start = ctx->color_start.p;
-        a.n_groups = ctx->counters.p + CNT_COLORS;
+        a.sched_color = ctx->con_sorted_color.p;
+        a.group_start = ctx->bin_base.p + n_keys;
+        a.n_groups = ctx->counters.p + CNT_GROUPS;
         a.serial_group = 64;
+        a.bin_ok = ctx->bin_tab.p + 3 * (size_t)(ctx->n_bodies / BIN_BLOCK + 1);
+        a.bin_lo = ctx->bin_tab.p + 1 * (size_t)(ctx->n_bodies / BIN_BLOCK + 1);
+        a.bin_hi = ctx->bin_tab.p + 2 * (size_t)(ctx->n_bodies / BIN_BLOCK + 1);
+        a.bin_base = a.group_start;
     }
     a.info = ctx->con_info.p;
     a.sc = ctx->scontacts.p;
@@ -751,14 +963,29 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     for (const SpaceParams &sp : ctx->spaces) a.iterations = std::max(a.iterations, sp.iterations);
     a.max_priority = nj ? ctx->max_priority : 1u;
     a.counters = ctx->counters.p;
-    int per_sm = 0;
-    void *kernel = ctx->h_ccd_ids.empty() ? (void *)k_solve<false> : (void *)k_solve<true>;
-    BPC_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)kernel, SV_THREADS, 0));
-    if (per_sm < 1) per_sm = 1;
-    if (per_sm > 8) per_sm = 8;
-    dim3 grid(ctx->sm_count * per_sm), block(SV_THREADS);
     void *args[] = { &a };
-    BPC_CHECK(cudaLaunchCooperativeKernel(kernel, grid, block, args, 0, st));
-    ctx->launches += 1;
+    void *kernels[2] = { ctx->h_ccd_ids.empty() ? (void *)k_presolve<false> : (void *)k_presolve<true>, (void *)k_sweeps };
+    for (int k = 0; k < 2; k++) {
+        int per_sm = 0;
+        BPC_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)kernels[k], SV_THREADS, 0));
+        if (per_sm < 1) per_sm = 1;
+        if (per_sm > 8) per_sm = 8;
+        dim3 grid(ctx->sm_count * per_sm), block(SV_THREADS);
+        BPC_CHECK(cudaLaunchCooperativeKernel(kernels[k], grid, block, args, 0, st));
+    }
+    ctx->launches += 2;
+    if (!ctx->n_forced_levels && ctx->n_bins) {
+        static bool attr_set = false;
+        size_t smem = (size_t)BIN_MAX_BODIES * SB_STRIDE * sizeof(float) + BIN_MAX_BODIES + BIN_MAX_CONS * sizeof(uint16_t) +
+                      (BIN_KEYS_SV + 1 + BIN_COLS_SV + 1) * sizeof(uint32_t);
+        smem = (smem + 15) & ~(size_t)15;
+        if (!attr_set) {
+            BPC_CHECK(cudaFuncSetAttribute(k_solve_bins, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set = true;
+        }
+        k_solve_bins<<<ctx->n_bins, SB_THREADS, smem, st>>>(a);
+        BPC_CHECK(cudaGetLastError());
+        ctx->launches += 1;
+    }
     return 0;
 }

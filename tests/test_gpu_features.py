@@ -222,13 +222,14 @@ def test_inactive_space_is_not_stepped_and_resumes_unchanged():
     assert not np.array_equal(now[~sp1], frozen[~sp1])            # the others did
     assert ps.stats()["active_objects"] <= int((~sp1 & (sc.bodies["mode"] >= 2)).sum())
     ps.space_set_active(1, True)
-    for _ in range(20):
-        ps.step(sc.dt)
-        twin.step(sc.dt)
-    # space 1 took its 20 steps later than its twin, from the same state with the same cached contacts
+    ps.step(sc.dt)
+    twin.step(sc.dt)
+    # space 1 takes its 51st step 20 steps later than its twin, from the same state with the same cached contacts; only the
+    # sweep order may differ (it depends on the pair counts of the other spaces)
     a = ps.bodies_read_state()[sp1]
     b = twin.bodies_read_state()[sp1]
-    assert np.allclose(a[:, 9:12], b[:, 9:12], atol=2e-3)         # (the sweep order depends on the other spaces' pair counts)
+    assert not np.array_equal(a, frozen[sp1])
+    assert np.allclose(a[:, 0:18], b[:, 0:18], atol=1e-3)
     ps.finish()
     twin.finish()
 
