@@ -183,6 +183,8 @@ extern "C" int bpc_get_stats(bpc_context *ctx, bpc_stats *out) {
     out->colors = ctx->n_forced_levels ? (int)ctx->n_forced_levels : (int)ctx->h_counters[CNT_COLORS];
     out->overflow = (int)ctx->h_counters[CNT_OVERFLOW];
     out->active_contacts = (int)ctx->h_counters[CNT_ACTIVE_CONTACTS];
+    out->full_pairs = (int)(ctx->h_counters[CNT_WORK] + ctx->h_counters[CNT_CWORK]);
+    out->barrier_constraints = ctx->n_forced_levels ? (int)ctx->n_forced : (int)ctx->h_counters[CNT_BARRIER_CONS];
     out->steps = (int)ctx->step_count;
     out->kernel_launches = (int)ctx->launches;
     return 0;

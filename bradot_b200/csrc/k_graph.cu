@@ -405,13 +405,17 @@ __global__ void __launch_bounds__(1024) k_bin_scan(uint32_t n_keys, const uint32
         run += hist[i];
     }
     if (t == 1023) base[n_keys] = part[1023];
+    __syncthreads();
     if (t < 32) { // number of grid-wide groups = colours in use on the barrier path
         uint32_t top_global = 0;
         for (uint32_t k = t; k < BIN_KEYS; k += 32) {
             if (hist[k]) top_global = max(top_global, k / 4 + 1);
         }
         for (int o = 16; o; o >>= 1) top_global = max(top_global, __shfl_xor_sync(0xffffffffu, top_global, o));
-        if (t == 0) counters[CNT_GROUPS] = top_global;
+        if (t == 0) {
+            counters[CNT_GROUPS] = top_global;
+            counters[CNT_BARRIER_CONS] = base[BIN_KEYS < n_keys ? BIN_KEYS : n_keys];
+        }
     }
 }
 
@@ -488,13 +492,13 @@ int bpc_launch_schedule(bpc_context *ctx) {
     uint32_t n_bins = n / BIN_BLOCK + 1;
     uint32_t n_keys = BIN_KEYS + n_bins;
     // (bodies with continuous collision detection have their velocities cut in global memory by the tunnelling test)
-    // Measured (C5, 10 colours): at 1.9 M constraints the barrier path is 10 % faster (190 k constraints per colour keep every
-    // SM busy between barriers), at 240 k constraints the bins are 28 % faster (24 k per colour: the grid mostly waits).  The
-    // last finished step's counts decide.
+    // Measured (C5, ~10 colours): at 1.9 M constraints the barrier path is 10 % faster (190 k constraints per colour keep every
+    // SM busy between barriers), at 0.95 M and 0.48 M the two are level, at 240 k the bins are 28 % faster (24 k per colour:
+    // less than one constraint per resident thread, the grid mostly waits).  The last finished step's counts decide.
     bool wanted = ctx->use_bins;
     if (wanted && ctx->h_counters[CNT_COLORS]) {
         uint64_t per_colour = (uint64_t)(ctx->h_counters[CNT_CONS] + nj) / ctx->h_counters[CNT_COLORS];
-        wanted = per_colour < (uint64_t)ctx->sm_count * 384u * 3u;
+        wanted = per_colour < (uint64_t)ctx->sm_count * 384u;
     }
     const bool bins = wanted && ctx->h_ccd_ids.empty();
     ctx->n_bins = bins ? n_bins : 0;

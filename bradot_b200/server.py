@@ -49,7 +49,8 @@ STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule"
 
 class Stats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in ("active_objects", "collision_pairs", "island_count", "contact_pairs",
-                                              "colors", "overflow", "steps", "kernel_launches", "active_contacts")]
+                                              "colors", "overflow", "steps", "kernel_launches", "active_contacts",
+                                              "full_pairs", "barrier_constraints")]
 
 
 class PhysicsError(RuntimeError):

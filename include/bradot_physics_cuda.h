@@ -93,6 +93,8 @@ typedef struct bpc_stats {
     int32_t steps;
     int32_t kernel_launches; /* kernels launched by the last bpc_step */
     int32_t active_contacts; /* contacts with positive depth handed to the solver this step */
+    int32_t full_pairs;      /* pairs that went through the full narrowphase pass (contact generation) this step */
+    int32_t barrier_constraints; /* constraints swept on the solver's grid-barrier path (the rest ran in solver bins) */
 } bpc_stats;
 
 /* ---- lifecycle: BradotPhysicsServer3D::init / finish (P3D/bradot_physics_server_3d.cpp:1628-1630, 1704-1706) */

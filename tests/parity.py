@@ -161,7 +161,8 @@ def teacher_forced(sc, steps, check_steps, import_order=True, dump=None):
     if dump is None:   # only the steps that are loaded or compared are dumped
         _, dump = run_oracle(sc, steps, dump_steps=[k for k in check_steps] + [k + 1 for k in check_steps], slim=True)
     ps = new_server(sc, dump)
-    worst = {"contact": 0.0, "state": 0.0, "pairs": 0, "colliding": 0, "contacts": 0, "items": 0.0, "item_pairs_differ": 0}
+    worst = {"contact": 0.0, "state": 0.0, "pairs": 0, "colliding": 0, "contacts": 0, "items": 0.0, "item_pairs_differ": 0,
+             "items_exact": 0.0, "stored_differ": 0, "stored_unexplained": 0, "moved": 0}
     for k in check_steps:
         assert k >= 1
         load_state(ps, dump, k)
@@ -202,6 +203,18 @@ def teacher_forced(sc, steps, check_steps, import_order=True, dump=None):
             moved = sc.bodies["mode"] >= scenes.MODE_RIGID
             worst["items"] = max(worst["items"], rel_err(it[moved, 0:12], rit[moved, 0:12], 1.0))
             worst["item_pairs_differ"] += int((it[moved, 12] != rit[moved, 12]).sum())
+            # the same, split: the exact shape AABB (must always agree) and the stored box.  A stored box may differ in ONE way:
+            # the reference re-stores an item whose new expanded box pokes out of its BVH leaf's bound even though the old stored
+            # box still encloses the exact one (core/math/bvh_public.inc:126); this backend has no such tree and keeps the old
+            # box (known deviations).  "Explained" = the GPU's box is the one that was loaded (kept), the reference's
+            # is a fresh one around its exact box.
+            worst["items_exact"] = max(worst["items_exact"], rel_err(it[moved, 0:6], rit[moved, 0:6], 1.0))
+            err = np.max(np.abs(it[:, 6:12].astype(np.float64) - rit[:, 6:12]) / np.maximum(np.abs(rit[:, 6:12]), 1.0), axis=1)
+            differ = moved & (err >= 1e-5)
+            kept = np.all(it[:, 6:12] == dump[("items", k)][:, 6:12], axis=1)
+            worst["stored_differ"] += int(differ.sum())
+            worst["stored_unexplained"] += int((differ & ~kept).sum())
+            worst["moved"] += int(moved.sum())
     ps.finish()
     return worst
 
