@@ -473,6 +473,7 @@ int bpc_wake_neighbours(bpc_context *ctx, const std::vector<uint32_t> &who) {
 }
 
 int bpc_joints_destroy_of_bodies(bpc_context *ctx, const std::vector<uint8_t> &gone);
+static void rebuild_exceptions(bpc_context *ctx);
 
 extern "C" int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n) {
     if (!ctx) return -1;
@@ -503,13 +504,12 @@ extern "C" int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n)
         ctx->free_slots.push_back(i);
         gone[i] = 1;
     }
-    // collision exceptions that name a destroyed body go with it
-    size_t before = ctx->h_except.size();
-    ctx->h_except.erase(std::remove_if(ctx->h_except.begin(), ctx->h_except.end(),
-                                       [&](uint64_t k) { return gone[(uint32_t)(k >> 32)] || gone[(uint32_t)k]; }),
-                        ctx->h_except.end());
-    if (ctx->h_except.size() != before) ctx->except_dirty = true;
+    // collision exceptions that name a destroyed body go with it (the joints' ones with their joints)
+    ctx->h_except_user.erase(std::remove_if(ctx->h_except_user.begin(), ctx->h_except_user.end(),
+                                            [&](uint64_t k) { return gone[(uint32_t)(k >> 32)] || gone[(uint32_t)k]; }),
+                             ctx->h_except_user.end());
     if (bpc_joints_destroy_of_bodies(ctx, gone)) return -1;
+    rebuild_exceptions(ctx);
     ctx->lists_dirty = true;
     return 0;
 }
@@ -530,7 +530,7 @@ static void joint_defaults(JointRec &j) {
 
 // collision exceptions are those of the live joints that ask for them
 static void rebuild_exceptions(bpc_context *ctx) {
-    ctx->h_except.clear();
+    ctx->h_except = ctx->h_except_user;
     ctx->max_priority = 1;
     for (const JointRec &j : ctx->h_joints) {
         if (j.flags & JF_DEAD) continue;
@@ -606,6 +606,20 @@ int bpc_joints_destroy_of_bodies(bpc_context *ctx, const std::vector<uint8_t> &g
     return 0;
 }
 
+extern "C" int bpc_bodies_set_exception(bpc_context *ctx, int body_a, int body_b, int excepted) {
+    if (!ctx) return -1;
+    if (body_a < 0 || body_b < 0 || (uint32_t)body_a >= ctx->n_bodies || (uint32_t)body_b >= ctx->n_bodies || body_a == body_b)
+        return fail(ctx, "bpc_bodies_set_exception: invalid body");
+    uint64_t key = ((uint64_t)std::min(body_a, body_b) << 32) | (uint32_t)std::max(body_a, body_b);
+    auto it = std::lower_bound(ctx->h_except_user.begin(), ctx->h_except_user.end(), key);
+    bool have = it != ctx->h_except_user.end() && *it == key;
+    if (excepted && !have) ctx->h_except_user.insert(it, key);
+    else if (!excepted && have) ctx->h_except_user.erase(it);
+    else return 0;
+    rebuild_exceptions(ctx);
+    return 0;
+}
+
 extern "C" int bpc_joint_count(bpc_context *ctx) { return ctx ? (int)ctx->h_joints.size() : -1; }
 
 // ---------------------------------------------------------------------------------------------- bulk state I/O
@@ -652,7 +666,8 @@ static int field_width(int field) {
         case BPC_FIELD_KINEMATIC_TARGET: return 12;
         case BPC_FIELD_KINEMATIC_VELOCITY: return 6;
         case BPC_FIELD_ITEM_BOX: return 14;
-        case BPC_FIELD_APPLIED_FORCE: return 6;
+        case BPC_FIELD_APPLIED_FORCE: case BPC_FIELD_CONSTANT_FORCE: return 6;
+        case BPC_FIELD_MASS_WORLD: return 13;
         default: return 0;
     }
 }
@@ -727,12 +742,24 @@ extern "C" int bpc_bodies_read(bpc_context *ctx, int field, int first, int n, fl
                 o[13] = (float)(first + i);
             }
         } break;
-        case BPC_FIELD_APPLIED_FORCE: {
+        case BPC_FIELD_APPLIED_FORCE:
+        case BPC_FIELD_CONSTANT_FORCE: {
             std::vector<BodyForces> h;
             if (fetch(ctx, h, ctx->forces, first, n)) return -1;
             for (int i = 0; i < n; i++) {
                 float *o = out + 6 * i;
-                o[0] = h[i].force.x; o[1] = h[i].force.y; o[2] = h[i].force.z; o[3] = h[i].torque.x; o[4] = h[i].torque.y; o[5] = h[i].torque.z;
+                const float4 &f = field == BPC_FIELD_APPLIED_FORCE ? h[i].force : h[i].cforce, &t = field == BPC_FIELD_APPLIED_FORCE ? h[i].torque : h[i].ctorque;
+                o[0] = f.x; o[1] = f.y; o[2] = f.z; o[3] = t.x; o[4] = t.y; o[5] = t.z;
+            }
+        } break;
+        case BPC_FIELD_MASS_WORLD: {
+            std::vector<BodyMassW> m;
+            if (fetch(ctx, m, ctx->massw, first, n)) return -1;
+            for (int i = 0; i < n; i++) {
+                float *o = out + 13 * i;
+                o[0] = m[i].i0.x; o[1] = m[i].i0.y; o[2] = m[i].i0.z; o[3] = m[i].i1.x; o[4] = m[i].i1.y; o[5] = m[i].i1.z;
+                o[6] = m[i].i2.x; o[7] = m[i].i2.y; o[8] = m[i].i2.z; o[9] = m[i].i0.w; o[10] = m[i].i1.w; o[11] = m[i].i2.w;
+                o[12] = m[i].m.x;
             }
         } break;
     }
@@ -835,6 +862,25 @@ extern "C" int bpc_bodies_write(bpc_context *ctx, int field, int first, int n, c
                 np[i] = (uint32_t)o[12];
             }
             if (store(ctx, h, ctx->items, first) || store(ctx, np, ctx->npairs, first)) return -1;
+        } break;
+        case BPC_FIELD_MASS_WORLD:
+            return fail(ctx, "bpc_bodies_write: BPC_FIELD_MASS_WORLD is derived from the transform and the mass properties (read only)");
+        case BPC_FIELD_CONSTANT_FORCE: {
+            std::vector<BodyForces> h;
+            std::vector<uint4> mt;
+            if (fetch(ctx, h, ctx->forces, first, n) || fetch(ctx, mt, ctx->meta, first, n)) return -1;
+            bool woke = false;
+            for (int i = 0; i < n; i++) {
+                const float *o = in + 6 * i;
+                h[i].cforce = make_float4(o[0], o[1], o[2], 0.f);
+                h[i].ctorque = make_float4(o[3], o[4], o[5], 0.f);
+                bool nz = o[0] != 0.f || o[1] != 0.f || o[2] != 0.f || o[3] != 0.f || o[4] != 0.f || o[5] != 0.f;
+                if (nz && (mt[i].x & 0xffu) >= MODE_RIGID && !((mt[i].x >> 8) & (BF_ACTIVE | BF_FROZEN))) {
+                    mt[i].x |= BF_ACTIVE << 8;
+                    woke = true;
+                }
+            }
+            if (store(ctx, h, ctx->forces, first) || (woke && store(ctx, mt, ctx->meta, first))) return -1;
         } break;
         case BPC_FIELD_APPLIED_FORCE: {
             if (staging_for(ctx, (size_t)n * 6)) return -1;

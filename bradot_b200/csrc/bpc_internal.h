@@ -242,6 +242,7 @@ struct bpc_context {
     // body pairs excepted from colliding (joint_disable_collisions_between_bodies / body_add_collision_exception)
     DevBuf<uint64_t> except_keys;
     std::vector<uint64_t> h_except;
+    std::vector<uint64_t> h_except_user; // body_add_collision_exception (sorted); h_except = these + the live joints' 
     uint32_t n_except = 0;
     bool except_dirty = false;
     uint32_t shape_type_mask = 0; // shape types present among the bodies (bit = ShapeType)

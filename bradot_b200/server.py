@@ -22,7 +22,8 @@ LIB_PATH = os.environ.get("BPC_LIBRARY", os.path.join(_HERE, "libbradot_physics_
 FIELD_TRANSFORM, FIELD_LINEAR_VELOCITY, FIELD_ANGULAR_VELOCITY, FIELD_ACTIVE = 0, 1, 2, 3
 FIELD_MASS_PROPS, FIELD_ITEM_BOX, FIELD_APPLIED_FORCE, FIELD_STILL_TIME = 4, 5, 6, 7
 FIELD_KINEMATIC_TARGET, FIELD_KINEMATIC_VELOCITY = 8, 9   # write only, kinematic bodies
-_FIELD_WIDTH = {0: 12, 1: 3, 2: 3, 3: 1, 4: 16, 5: 14, 6: 6, 7: 1, 8: 12, 9: 6}
+FIELD_CONSTANT_FORCE, FIELD_MASS_WORLD = 10, 11
+_FIELD_WIDTH = {0: 12, 1: 3, 2: 3, 3: 1, 4: 16, 5: 14, 6: 6, 7: 1, 8: 12, 9: 6, 10: 6, 11: 13}
 
 SPACE_PARAM_CONTACT_RECYCLE_RADIUS, SPACE_PARAM_CONTACT_MAX_SEPARATION = 0, 1
 SPACE_PARAM_CONTACT_MAX_ALLOWED_PENETRATION, SPACE_PARAM_CONTACT_DEFAULT_BIAS = 2, 3
@@ -41,7 +42,7 @@ EXPORTS = [
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
     "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
     "bpc_bodies_set_state", "bpc_bodies_read_slots", "bpc_bodies_write_slots", "bpc_bodies_read_state", "bpc_reserve",
-    "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_test_segment_math",
+    "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_test_segment_math", "bpc_bodies_set_exception",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
@@ -95,6 +96,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_bodies_write_slots.argtypes = [vp, ci, vp, ci, vp]
     lib.bpc_bodies_read_state.argtypes = [vp, ci, ci, vp]
     lib.bpc_reserve.argtypes = [vp, ci, ci]
+    lib.bpc_bodies_set_exception.argtypes = [vp, ci, ci, ci]
     lib.bpc_test_segment_math.argtypes = [vp, ci, ci, vp, vp]
     lib.bpc_step.argtypes = [vp, cf]
     lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
@@ -258,6 +260,9 @@ class PhysicsServerCUDA:
         out = np.zeros((len(r), 6 if op == 0 else 3), np.float32)
         self._check(self.lib.bpc_test_segment_math(self.ctx, int(op), len(r), _ptr(r), _ptr(out)))
         return out
+
+    def body_set_collision_exception(self, a, b, excepted=True):
+        self._check(self.lib.bpc_bodies_set_exception(self.ctx, int(a), int(b), 1 if excepted else 0))
 
     def reserve(self, bodies, pairs):
         self._check(self.lib.bpc_reserve(self.ctx, int(bodies), int(pairs)))

@@ -6,6 +6,7 @@
 
 #include "core/math/convex_hull.h"
 #include "core/math/geometry_3d.h"
+#include "core/object/object.h"
 
 static void _xf_to_floats(const Transform3D &p_xf, float *r_out) {
 	for (int r = 0; r < 3; r++) {
@@ -137,6 +138,8 @@ RID BradotPhysicsServerCUDA::space_create() {
 	ERR_FAIL_NULL_V_MSG(ctx, RID(), "BradotPhysicsCUDA: init() failed, no CUDA device.");
 	Space *space = memnew(Space);
 	space->handle = bpc_space_create(ctx);
+	// a new space is inactive until space_set_active(true) (bradot_physics_server_3d.cpp:144-170)
+	bpc_space_set_active(ctx, space->handle, 0);
 	return space_owner.make_rid(space);
 }
 
@@ -171,7 +174,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 	r_hit.resize(n);
 	int hits = 0;
 	for (int i = 0; i < n; i++) {
-		r_hit[i] = out[i].hit != 0 && out[i].body >= 0 && (uint32_t)out[i].body < server->body_of_slot.size();
+		r_hit[i] = out[i].hit != 0 && out[i].body >= 0 && (uint32_t)out[i].body < server->body_of_slot.size() && server->body_of_slot[out[i].body];
 		if (!r_hit[i]) {
 			continue;
 		}
@@ -180,8 +183,8 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 		r.position = Vector3(out[i].position[0], out[i].position[1], out[i].position[2]);
 		r.normal = Vector3(out[i].normal[0], out[i].normal[1], out[i].normal[2]);
 		r.rid = server->body_of_slot[out[i].body]->self;
-		r.collider_id = ObjectID(); // body_attach_object_instance_id is not carried yet
-		r.collider = nullptr;
+		r.collider_id = server->body_of_slot[out[i].body]->instance_id;
+		r.collider = r.collider_id.is_valid() ? ObjectDB::get_instance(r.collider_id) : nullptr;
 		r.shape = 0;
 		r.face_index = -1;
 	}
@@ -203,12 +206,12 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_
 	ERR_FAIL_COND_V_MSG(bpc_space_intersect_points(server->ctx, space_handle, 1, p, p_parameters.collision_mask, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
 	int cc = 0;
 	for (int i = 0; i < count; i++) {
-		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size()) {
+		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size() || !server->body_of_slot[slots[i]]) {
 			continue;
 		}
 		r_results[cc].rid = server->body_of_slot[slots[i]]->self;
-		r_results[cc].collider_id = ObjectID();
-		r_results[cc].collider = nullptr;
+		r_results[cc].collider_id = server->body_of_slot[slots[i]]->instance_id;
+		r_results[cc].collider = r_results[cc].collider_id.is_valid() ? ObjectDB::get_instance(r_results[cc].collider_id) : nullptr;
 		r_results[cc].shape = 0;
 		cc++;
 	}
@@ -236,13 +239,13 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_
 	ERR_FAIL_COND_V_MSG(bpc_space_intersect_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
 	int cc = 0;
 	for (int i = 0; i < count; i++) {
-		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size()) {
+		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size() || !server->body_of_slot[slots[i]]) {
 			continue;
 		}
 		if (r_results) {
 			r_results[cc].rid = server->body_of_slot[slots[i]]->self;
-			r_results[cc].collider_id = ObjectID();
-			r_results[cc].collider = nullptr;
+			r_results[cc].collider_id = server->body_of_slot[slots[i]]->instance_id;
+			r_results[cc].collider = r_results[cc].collider_id.is_valid() ? ObjectDB::get_instance(r_results[cc].collider_id) : nullptr;
 			r_results[cc].shape = 0;
 		}
 		cc++;
@@ -298,7 +301,8 @@ bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_par
 void BradotPhysicsServerCUDA::space_set_active(RID p_space, bool p_active) {
 	Space *space = space_owner.get_or_null(p_space);
 	ERR_FAIL_NULL(space);
-	space->active = p_active; // every created space is stepped by bpc_step; inactive spaces are a TODO of the C ABI
+	space->active = p_active;
+	ERR_FAIL_COND_MSG(bpc_space_set_active(ctx, space->handle, p_active ? 1 : 0) < 0, bpc_last_error(ctx));
 }
 
 bool BradotPhysicsServerCUDA::space_is_active(RID p_space) const {
@@ -311,9 +315,9 @@ void BradotPhysicsServerCUDA::space_set_param(RID p_space, SpaceParameter p_para
 	Space *space = space_owner.get_or_null(p_space);
 	ERR_FAIL_NULL(space);
 	ERR_FAIL_INDEX((int)p_param, 8);
-	space->params[p_param] = p_value;
 	// SpaceParameter values and BPC_SPACE_* values are the same numbers (servers/physics_server_3d.h:283-292)
-	bpc_space_set_param(ctx, space->handle, (int)p_param, p_value);
+	ERR_FAIL_COND_MSG(bpc_space_set_param(ctx, space->handle, (int)p_param, p_value) < 0, bpc_last_error(ctx));
+	space->params[p_param] = p_value;
 }
 
 real_t BradotPhysicsServerCUDA::space_get_param(RID p_space, SpaceParameter p_param) const {
@@ -332,13 +336,83 @@ RID BradotPhysicsServerCUDA::body_create() {
 	return rid;
 }
 
+void BradotPhysicsServerCUDA::_fill_desc(const Body *p_body, bpc_body_desc &r_desc) {
+	const Body *b = p_body;
+	r_desc = {};
+	const Space *space = space_owner.get_or_null(b->space);
+	Shape *shape = shape_owner.get_or_null(b->shape);
+	r_desc.space = space ? space->handle : 0;
+	r_desc.mode = (uint32_t)b->mode;
+	r_desc.shape = shape ? _shape_handle(shape) : 0;
+	r_desc.flags = (b->can_sleep ? 1 : 0) | (b->ccd ? 2 : 0) | (b->lin_damp_replace ? 16 : 0) | (b->ang_damp_replace ? 32 : 0) |
+			(b->omit_force_integration ? 64 : 0) | ((b->locked_axis & 63) << 8);
+	_xf_to_floats(b->xf, r_desc.xf);
+	_xf_to_floats(b->shape_xf, r_desc.shape_xf);
+	r_desc.linvel[0] = b->linvel.x; r_desc.linvel[1] = b->linvel.y; r_desc.linvel[2] = b->linvel.z;
+	r_desc.angvel[0] = b->angvel.x; r_desc.angvel[1] = b->angvel.y; r_desc.angvel[2] = b->angvel.z;
+	r_desc.mass = b->mass; r_desc.friction = b->friction; r_desc.bounce = b->bounce; r_desc.gravity_scale = b->gravity_scale;
+	r_desc.lin_damp = b->lin_damp; r_desc.ang_damp = b->ang_damp; r_desc.layer = b->layer; r_desc.mask = b->mask;
+}
+
+// A property that is part of the body's description changed.  Before the upload it simply sits in the host record; after it
+// the body is re-described in bulk before the next step or query (bpc_bodies_update keeps its transform, velocities and
+// sleep state).
+void BradotPhysicsServerCUDA::_body_changed(Body *p_body) {
+	if (p_body->slot >= 0 && !p_body->dirty) {
+		p_body->dirty = true;
+		dirty_bodies.push_back(p_body);
+	}
+}
+
+void BradotPhysicsServerCUDA::_body_leave_space(Body *p_body) {
+	if (p_body->pending) {
+		pending_bodies.erase(p_body);
+		p_body->pending = false;
+	}
+	if (p_body->dirty) {
+		dirty_bodies.erase(p_body);
+		p_body->dirty = false;
+	}
+	if (p_body->slot >= 0) {
+		int32_t slot = p_body->slot;
+		// joints attached to the body go with its slot on the GPU side; their host records fall back to "not uploaded"
+		List<RID> joints;
+		joint_owner.get_owned_list(&joints);
+		for (const RID &jr : joints) {
+			Joint *j = joint_owner.get_or_null(jr);
+			if (j && j->handle >= 0 && (j->a == p_body->self || j->b == p_body->self)) {
+				j->handle = -1;
+			}
+		}
+		ERR_FAIL_COND_MSG(bpc_bodies_destroy(ctx, &slot, 1) < 0, bpc_last_error(ctx));
+		body_of_slot[slot] = nullptr;
+		p_body->slot = -1;
+		state_cache_valid = false;
+	}
+}
+
 void BradotPhysicsServerCUDA::body_set_space(RID p_body, RID p_space) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
-	ERR_FAIL_COND_MSG(body->slot >= 0, "BradotPhysicsCUDA: moving a body between spaces is not supported yet.");
 	if (p_space.is_valid()) {
 		ERR_FAIL_NULL(space_owner.get_or_null(p_space));
-		body->space = p_space;
+	}
+	if (body->space == p_space) {
+		return; // pointless (bradot_physics_server_3d.cpp:461-463)
+	}
+	// leaving a space: the body's slot is freed and its pairs go with the next step
+	if (body->slot >= 0) {
+		const float *st = _body_cached_state(body);
+		if (st) { // it takes its state along
+			body->xf = _floats_to_xf(st);
+			body->linvel = Vector3(st[12], st[13], st[14]);
+			body->angvel = Vector3(st[15], st[16], st[17]);
+		}
+	}
+	_body_leave_space(body);
+	body->space = p_space;
+	if (p_space.is_valid() && !body->pending) {
+		body->pending = true;
 		pending_bodies.push_back(body);
 	}
 }
@@ -352,8 +426,11 @@ RID BradotPhysicsServerCUDA::body_get_space(RID p_body) const {
 void BradotPhysicsServerCUDA::body_set_mode(RID p_body, BodyMode p_mode) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
-	ERR_FAIL_COND_MSG(body->slot >= 0, "BradotPhysicsCUDA: the body mode is fixed once the body is in a space.");
+	if (body->mode == p_mode) {
+		return;
+	}
 	body->mode = p_mode;
+	_body_changed(body);
 }
 
 PhysicsServer3D::BodyMode BradotPhysicsServerCUDA::body_get_mode(RID p_body) const {
@@ -370,6 +447,61 @@ void BradotPhysicsServerCUDA::body_add_shape(RID p_body, RID p_shape, const Tran
 	ERR_FAIL_COND_MSG(p_disabled, "BradotPhysicsCUDA: disabled shapes are not supported yet.");
 	body->shape = p_shape;
 	body->shape_xf = p_transform;
+	_body_changed(body);
+}
+
+void BradotPhysicsServerCUDA::body_set_shape(RID p_body, int p_shape_idx, RID p_shape) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
+	ERR_FAIL_COND(p_shape_idx != 0 || !body->shape.is_valid());
+	body->shape = p_shape;
+	_body_changed(body);
+}
+
+void BradotPhysicsServerCUDA::body_set_shape_transform(RID p_body, int p_shape_idx, const Transform3D &p_transform) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	ERR_FAIL_COND(p_shape_idx != 0 || !body->shape.is_valid());
+	body->shape_xf = p_transform;
+	_body_changed(body);
+}
+
+RID BradotPhysicsServerCUDA::body_get_shape(RID p_body, int p_shape_idx) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, RID());
+	ERR_FAIL_COND_V(p_shape_idx != 0 || !body->shape.is_valid(), RID());
+	return body->shape;
+}
+
+Transform3D BradotPhysicsServerCUDA::body_get_shape_transform(RID p_body, int p_shape_idx) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, Transform3D());
+	ERR_FAIL_COND_V(p_shape_idx != 0 || !body->shape.is_valid(), Transform3D());
+	return body->shape_xf;
+}
+
+// A body without its shape takes no part in the step: it leaves the GPU side until it is given a shape again.
+void BradotPhysicsServerCUDA::body_remove_shape(RID p_body, int p_shape_idx) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	ERR_FAIL_COND(p_shape_idx != 0 || !body->shape.is_valid());
+	body_clear_shapes(p_body);
+}
+
+void BradotPhysicsServerCUDA::body_clear_shapes(RID p_body) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	if (!body->shape.is_valid()) {
+		return;
+	}
+	bool in_space = body->slot >= 0 || body->pending;
+	_body_leave_space(body);
+	body->shape = RID();
+	if (in_space && !body->pending) { // re-uploaded by _flush_pending once it has a shape again
+		body->pending = true;
+		pending_bodies.push_back(body);
+	}
 }
 
 int BradotPhysicsServerCUDA::body_get_shape_count(RID p_body) const {
@@ -378,10 +510,23 @@ int BradotPhysicsServerCUDA::body_get_shape_count(RID p_body) const {
 	return body->shape.is_valid() ? 1 : 0;
 }
 
+void BradotPhysicsServerCUDA::body_attach_object_instance_id(RID p_body, ObjectID p_id) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->instance_id = p_id; // host-side only: query results are mapped back through body_of_slot
+}
+
+ObjectID BradotPhysicsServerCUDA::body_get_object_instance_id(RID p_body) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, ObjectID());
+	return body->instance_id;
+}
+
 void BradotPhysicsServerCUDA::body_set_collision_layer(RID p_body, uint32_t p_layer) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
 	body->layer = p_layer;
+	_body_changed(body);
 }
 uint32_t BradotPhysicsServerCUDA::body_get_collision_layer(RID p_body) const {
 	const Body *body = body_owner.get_or_null(p_body);
@@ -392,6 +537,7 @@ void BradotPhysicsServerCUDA::body_set_collision_mask(RID p_body, uint32_t p_mas
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
 	body->mask = p_mask;
+	_body_changed(body);
 }
 uint32_t BradotPhysicsServerCUDA::body_get_collision_mask(RID p_body) const {
 	const Body *body = body_owner.get_or_null(p_body);
@@ -402,7 +548,6 @@ uint32_t BradotPhysicsServerCUDA::body_get_collision_mask(RID p_body) const {
 void BradotPhysicsServerCUDA::body_set_param(RID p_body, BodyParameter p_param, const Variant &p_value) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
-	ERR_FAIL_COND_MSG(body->slot >= 0, "BradotPhysicsCUDA: body parameters are fixed once the body is in a space (bulk upload).");
 	switch (p_param) {
 		case BODY_PARAM_BOUNCE: body->bounce = p_value; break;
 		case BODY_PARAM_FRICTION: body->friction = p_value; break;
@@ -414,9 +559,13 @@ void BradotPhysicsServerCUDA::body_set_param(RID p_body, BodyParameter p_param, 
 		case BODY_PARAM_GRAVITY_SCALE: body->gravity_scale = p_value; break;
 		case BODY_PARAM_LINEAR_DAMP: body->lin_damp = p_value; break;
 		case BODY_PARAM_ANGULAR_DAMP: body->ang_damp = p_value; break;
+		case BODY_PARAM_LINEAR_DAMP_MODE: body->lin_damp_replace = (int)p_value == BODY_DAMP_MODE_REPLACE; break;
+		case BODY_PARAM_ANGULAR_DAMP_MODE: body->ang_damp_replace = (int)p_value == BODY_DAMP_MODE_REPLACE; break;
 		default:
-			BPC_UNSUPPORTED("body_set_param(inertia / centre of mass / damp modes)");
+			BPC_UNSUPPORTED("body_set_param(inertia / centre of mass)");
+			return;
 	}
+	_body_changed(body);
 }
 
 Variant BradotPhysicsServerCUDA::body_get_param(RID p_body, BodyParameter p_param) const {
@@ -429,93 +578,577 @@ Variant BradotPhysicsServerCUDA::body_get_param(RID p_body, BodyParameter p_para
 		case BODY_PARAM_GRAVITY_SCALE: return body->gravity_scale;
 		case BODY_PARAM_LINEAR_DAMP: return body->lin_damp;
 		case BODY_PARAM_ANGULAR_DAMP: return body->ang_damp;
+		case BODY_PARAM_LINEAR_DAMP_MODE: return body->lin_damp_replace ? BODY_DAMP_MODE_REPLACE : BODY_DAMP_MODE_COMBINE;
+		case BODY_PARAM_ANGULAR_DAMP_MODE: return body->ang_damp_replace ? BODY_DAMP_MODE_REPLACE : BODY_DAMP_MODE_COMBINE;
 		default: return Variant();
 	}
 }
 
+// The body's row of the state read back at the last flush_queries(), or nullptr when there is none (then getters ask the GPU).
+const float *BradotPhysicsServerCUDA::_body_cached_state(const Body *p_body) {
+	if (!state_cache_valid || p_body->slot < 0 || (uint32_t)(p_body->slot + 1) * 19 > state_cache.size()) {
+		return nullptr;
+	}
+	return &state_cache[p_body->slot * 19];
+}
+
+// body_set_state: on an uploaded body it runs on the GPU with the reference's side effects (bpc_bodies_set_state restates
+// BradotBody3D::set_state, bradot_body_3d.cpp:352-417: wake-ups, orthonormalised transform, broadphase box, neighbours of a
+// moved static body)
 void BradotPhysicsServerCUDA::body_set_state(RID p_body, BodyState p_state, const Variant &p_variant) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
-	float f[12];
+	float f[12] = {};
 	switch (p_state) {
 		case BODY_STATE_TRANSFORM: {
 			body->xf = p_variant;
-			if (body->slot >= 0) {
-				_xf_to_floats(body->xf, f);
-				// a kinematic body is told where to be after the next step (new_transform, bradot_body_3d.cpp:355-364)
-				bpc_bodies_write(ctx, body->mode == BODY_MODE_KINEMATIC ? BPC_FIELD_KINEMATIC_TARGET : BPC_FIELD_TRANSFORM, body->slot, 1, f);
-			}
+			_xf_to_floats(body->xf, f);
 		} break;
 		case BODY_STATE_LINEAR_VELOCITY:
 		case BODY_STATE_ANGULAR_VELOCITY: {
 			Vector3 v = p_variant;
 			(p_state == BODY_STATE_LINEAR_VELOCITY ? body->linvel : body->angvel) = v;
-			if (body->slot >= 0 && body->mode == BODY_MODE_KINEMATIC) {
-				// constant_linear_velocity / constant_angular_velocity (bradot_body_3d.cpp:383-393)
-				f[0] = body->linvel.x; f[1] = body->linvel.y; f[2] = body->linvel.z;
-				f[3] = body->angvel.x; f[4] = body->angvel.y; f[5] = body->angvel.z;
-				bpc_bodies_write(ctx, BPC_FIELD_KINEMATIC_VELOCITY, body->slot, 1, f);
-			} else if (body->slot >= 0) {
-				f[0] = v.x;
-				f[1] = v.y;
-				f[2] = v.z;
-				bpc_bodies_write(ctx, p_state == BODY_STATE_LINEAR_VELOCITY ? BPC_FIELD_LINEAR_VELOCITY : BPC_FIELD_ANGULAR_VELOCITY, body->slot, 1, f);
-			}
+			f[0] = v.x;
+			f[1] = v.y;
+			f[2] = v.z;
 		} break;
-		case BODY_STATE_SLEEPING: {
-			if (body->slot >= 0) {
-				f[0] = bool(p_variant) ? 0.f : 1.f;
-				bpc_bodies_write(ctx, BPC_FIELD_ACTIVE, body->slot, 1, f);
-			}
-		} break;
+		case BODY_STATE_SLEEPING:
+			f[0] = bool(p_variant) ? 1.f : 0.f;
+			break;
 		case BODY_STATE_CAN_SLEEP:
 			body->can_sleep = p_variant;
+			f[0] = body->can_sleep ? 1.f : 0.f;
 			break;
+	}
+	if (body->slot < 0) {
+		return;
+	}
+	int32_t slot = body->slot;
+	ERR_FAIL_COND_MSG(bpc_bodies_set_state(ctx, (int)p_state, &slot, 1, f) < 0, bpc_last_error(ctx));
+	// keep the read-back copy in step with what was just set (a callback may set and then get)
+	float *st = state_cache_valid && (uint32_t)(slot + 1) * 19 <= state_cache.size() ? &state_cache[slot * 19] : nullptr;
+	if (st) {
+		switch (p_state) {
+			case BODY_STATE_TRANSFORM: {
+				Transform3D t = body->xf;
+				if (body->mode >= BODY_MODE_RIGID) {
+					t.orthonormalize();
+				}
+				if (body->mode != BODY_MODE_KINEMATIC) {
+					_xf_to_floats(t, st);
+				}
+			} break;
+			case BODY_STATE_LINEAR_VELOCITY: st[12] = f[0]; st[13] = f[1]; st[14] = f[2]; break;
+			case BODY_STATE_ANGULAR_VELOCITY: st[15] = f[0]; st[16] = f[1]; st[17] = f[2]; break;
+			case BODY_STATE_SLEEPING:
+				if (body->mode >= BODY_MODE_RIGID) {
+					st[18] = f[0] != 0.f ? 0.f : 1.f;
+					if (f[0] != 0.f) {
+						for (int k = 12; k < 18; k++) {
+							st[k] = 0.f;
+						}
+					}
+				}
+				break;
+			default:
+				break;
+		}
+		if (p_state != BODY_STATE_SLEEPING && p_state != BODY_STATE_CAN_SLEEP && body->mode >= BODY_MODE_RIGID) {
+			st[18] = 1.f;
+		}
 	}
 }
 
 Variant BradotPhysicsServerCUDA::body_get_state(RID p_body, BodyState p_state) const {
 	const Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL_V(body, Variant());
-	float f[12];
-	switch (p_state) {
-		case BODY_STATE_TRANSFORM:
-			if (body->slot < 0) {
-				return body->xf;
-			}
-			ERR_FAIL_COND_V_MSG(bpc_bodies_read(ctx, BPC_FIELD_TRANSFORM, body->slot, 1, f) < 0, Variant(), bpc_last_error(ctx));
-			return _floats_to_xf(f);
-		case BODY_STATE_LINEAR_VELOCITY:
-		case BODY_STATE_ANGULAR_VELOCITY:
-			if (body->slot < 0) {
-				return p_state == BODY_STATE_LINEAR_VELOCITY ? body->linvel : body->angvel;
-			}
-			ERR_FAIL_COND_V_MSG(bpc_bodies_read(ctx, p_state == BODY_STATE_LINEAR_VELOCITY ? BPC_FIELD_LINEAR_VELOCITY : BPC_FIELD_ANGULAR_VELOCITY, body->slot, 1, f) < 0,
-					Variant(), bpc_last_error(ctx));
-			return Vector3(f[0], f[1], f[2]);
-		case BODY_STATE_SLEEPING:
-			if (body->slot < 0) {
-				return false;
-			}
-			bpc_bodies_read(ctx, BPC_FIELD_ACTIVE, body->slot, 1, f);
-			return f[0] == 0.f;
-		case BODY_STATE_CAN_SLEEP:
-			return body->can_sleep;
+	if (p_state == BODY_STATE_CAN_SLEEP) {
+		return body->can_sleep;
 	}
-	return Variant();
+	if (body->slot < 0) {
+		switch (p_state) {
+			case BODY_STATE_TRANSFORM: return body->xf;
+			case BODY_STATE_LINEAR_VELOCITY: return body->linvel;
+			case BODY_STATE_ANGULAR_VELOCITY: return body->angvel;
+			default: return false;
+		}
+	}
+	float row[19];
+	const float *st = const_cast<BradotPhysicsServerCUDA *>(this)->_body_cached_state(body);
+	if (!st) {
+		ERR_FAIL_COND_V_MSG(bpc_bodies_read_state(ctx, body->slot, 1, row) < 0, Variant(), bpc_last_error(ctx));
+		st = row;
+	}
+	switch (p_state) {
+		case BODY_STATE_TRANSFORM: return _floats_to_xf(st);
+		case BODY_STATE_LINEAR_VELOCITY: return Vector3(st[12], st[13], st[14]);
+		case BODY_STATE_ANGULAR_VELOCITY: return Vector3(st[15], st[16], st[17]);
+		case BODY_STATE_SLEEPING: return st[18] == 0.f;
+		default: return Variant();
+	}
+}
+
+void BradotPhysicsServerCUDA::body_set_enable_continuous_collision_detection(RID p_body, bool p_enable) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->ccd = p_enable;
+	_body_changed(body);
+}
+
+bool BradotPhysicsServerCUDA::body_is_continuous_collision_detection_enabled(RID p_body) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, false);
+	return body->ccd;
+}
+
+void BradotPhysicsServerCUDA::body_set_axis_lock(RID p_body, BodyAxis p_axis, bool p_lock) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->locked_axis = p_lock ? (body->locked_axis | (uint32_t)p_axis) : (body->locked_axis & ~(uint32_t)p_axis);
+	_body_changed(body);
+	if (body->slot >= 0) { // body->wakeup() (bradot_physics_server_3d.cpp:820-826)
+		body_set_state(p_body, BODY_STATE_SLEEPING, false);
+	}
+}
+
+bool BradotPhysicsServerCUDA::body_is_axis_locked(RID p_body, BodyAxis p_axis) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, false);
+	return body->locked_axis & (uint32_t)p_axis;
+}
+
+void BradotPhysicsServerCUDA::body_set_omit_force_integration(RID p_body, bool p_omit) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->omit_force_integration = p_omit;
+	_body_changed(body);
+}
+
+bool BradotPhysicsServerCUDA::body_is_omitting_force_integration(RID p_body) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, false);
+	return body->omit_force_integration;
+}
+
+// body_add_collision_exception (bradot_physics_server_3d.cpp:690-720): one-sided in the reference's bookkeeping, symmetric
+// in effect (BradotBodyPair3D::setup skips the pair if either body excepts the other, bradot_body_pair_3d.cpp:267-270)
+void BradotPhysicsServerCUDA::body_add_collision_exception(RID p_body, RID p_body_b) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body_b));
+	if (!body->exceptions.has(p_body_b)) {
+		body->exceptions.push_back(p_body_b);
+	}
+	_flush_pending();
+	Body *other = body_owner.get_or_null(p_body_b);
+	if (body->slot >= 0 && other->slot >= 0) {
+		bpc_bodies_set_exception(ctx, body->slot, other->slot, 1);
+	}
+	if (body->slot >= 0) {
+		body_set_state(p_body, BODY_STATE_SLEEPING, false); // body->wakeup()
+	}
+}
+
+void BradotPhysicsServerCUDA::body_remove_collision_exception(RID p_body, RID p_body_b) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->exceptions.erase(p_body_b);
+	Body *other = body_owner.get_or_null(p_body_b);
+	if (other && body->slot >= 0 && other->slot >= 0 && !other->exceptions.has(p_body)) {
+		bpc_bodies_set_exception(ctx, body->slot, other->slot, 0);
+	}
+	if (body->slot >= 0) {
+		body_set_state(p_body, BODY_STATE_SLEEPING, false);
+	}
+}
+
+void BradotPhysicsServerCUDA::body_get_collision_exceptions(RID p_body, List<RID> *p_exceptions) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	for (const RID &r : body->exceptions) {
+		p_exceptions->push_back(r);
+	}
+}
+
+/* forces and impulses (bradot_physics_server_3d.cpp:827-940, bradot_body_3d.h:228-281) */
+
+void BradotPhysicsServerCUDA::_body_push(Body *p_body) {
+	if (!p_body->pushed) {
+		p_body->pushed = true;
+		pushed_bodies.push_back(p_body);
+	}
+}
+
+// world inverse inertia tensor, world-oriented centre of mass and inverse mass as the GPU holds them
+bool BradotPhysicsServerCUDA::_body_mass_world(const Body *p_body, Basis &r_iinv, Vector3 &r_com, real_t &r_inv_mass) const {
+	if (p_body->slot < 0) {
+		return false;
+	}
+	float m[13];
+	ERR_FAIL_COND_V_MSG(bpc_bodies_read(ctx, BPC_FIELD_MASS_WORLD, p_body->slot, 1, m) < 0, false, bpc_last_error(ctx));
+	r_iinv = Basis(m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8]);
+	r_com = Vector3(m[9], m[10], m[11]);
+	r_inv_mass = m[12];
+	return true;
+}
+
+void BradotPhysicsServerCUDA::body_apply_central_impulse(RID p_body, const Vector3 &p_impulse) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	_flush_pending();
+	Basis iinv;
+	Vector3 com;
+	real_t im = 0;
+	ERR_FAIL_COND_MSG(!_body_mass_world(body, iinv, com, im), "BradotPhysicsCUDA: impulses need a body that is in a space.");
+	Vector3 v = body_get_state(p_body, BODY_STATE_LINEAR_VELOCITY);
+	body_set_state(p_body, BODY_STATE_LINEAR_VELOCITY, v + p_impulse * im); // wakes the body, as body->wakeup() does
+}
+
+void BradotPhysicsServerCUDA::body_apply_impulse(RID p_body, const Vector3 &p_impulse, const Vector3 &p_position) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	_flush_pending();
+	Basis iinv;
+	Vector3 com;
+	real_t im = 0;
+	ERR_FAIL_COND_MSG(!_body_mass_world(body, iinv, com, im), "BradotPhysicsCUDA: impulses need a body that is in a space.");
+	Vector3 v = body_get_state(p_body, BODY_STATE_LINEAR_VELOCITY), w = body_get_state(p_body, BODY_STATE_ANGULAR_VELOCITY);
+	body_set_state(p_body, BODY_STATE_LINEAR_VELOCITY, v + p_impulse * im);
+	body_set_state(p_body, BODY_STATE_ANGULAR_VELOCITY, w + iinv.xform((p_position - com).cross(p_impulse)));
+}
+
+void BradotPhysicsServerCUDA::body_apply_torque_impulse(RID p_body, const Vector3 &p_impulse) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	_flush_pending();
+	Basis iinv;
+	Vector3 com;
+	real_t im = 0;
+	ERR_FAIL_COND_MSG(!_body_mass_world(body, iinv, com, im), "BradotPhysicsCUDA: impulses need a body that is in a space.");
+	Vector3 w = body_get_state(p_body, BODY_STATE_ANGULAR_VELOCITY);
+	body_set_state(p_body, BODY_STATE_ANGULAR_VELOCITY, w + iinv.xform(p_impulse));
+}
+
+// body_apply_central_force / body_apply_force / body_apply_torque: accumulated on the host, handed to the GPU in ONE
+// scattered write for all pushed bodies before the step (a non-zero row wakes its body there)
+void BradotPhysicsServerCUDA::body_apply_central_force(RID p_body, const Vector3 &p_force) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	_body_push(body);
+	body->applied_force += p_force;
+}
+
+void BradotPhysicsServerCUDA::body_apply_force(RID p_body, const Vector3 &p_force, const Vector3 &p_position) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	_flush_pending();
+	Basis iinv;
+	Vector3 com;
+	real_t im = 0;
+	_body_mass_world(body, iinv, com, im);
+	_body_push(body);
+	body->applied_force += p_force;
+	body->applied_torque += (p_position - com).cross(p_force);
+}
+
+void BradotPhysicsServerCUDA::body_apply_torque(RID p_body, const Vector3 &p_torque) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	_body_push(body);
+	body->applied_torque += p_torque;
+}
+
+static void _write_constant(bpc_context *ctx, int p_slot, const Vector3 &p_f, const Vector3 &p_t) {
+	float f[6] = { (float)p_f.x, (float)p_f.y, (float)p_f.z, (float)p_t.x, (float)p_t.y, (float)p_t.z };
+	bpc_bodies_write(ctx, BPC_FIELD_CONSTANT_FORCE, p_slot, 1, f);
+}
+
+void BradotPhysicsServerCUDA::body_add_constant_central_force(RID p_body, const Vector3 &p_force) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body_set_constant_force(p_body, body->constant_force + p_force);
+}
+
+void BradotPhysicsServerCUDA::body_add_constant_force(RID p_body, const Vector3 &p_force, const Vector3 &p_position) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	_flush_pending();
+	Basis iinv;
+	Vector3 com;
+	real_t im = 0;
+	_body_mass_world(body, iinv, com, im);
+	body->constant_torque += (p_position - com).cross(p_force);
+	body_set_constant_force(p_body, body->constant_force + p_force);
+}
+
+void BradotPhysicsServerCUDA::body_add_constant_torque(RID p_body, const Vector3 &p_torque) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body_set_constant_torque(p_body, body->constant_torque + p_torque);
+}
+
+void BradotPhysicsServerCUDA::body_set_constant_force(RID p_body, const Vector3 &p_force) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->constant_force = p_force;
+	_flush_pending();
+	if (body->slot >= 0) {
+		_write_constant(ctx, body->slot, body->constant_force, body->constant_torque);
+	}
+}
+
+Vector3 BradotPhysicsServerCUDA::body_get_constant_force(RID p_body) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, Vector3());
+	return body->constant_force;
+}
+
+void BradotPhysicsServerCUDA::body_set_constant_torque(RID p_body, const Vector3 &p_torque) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->constant_torque = p_torque;
+	_flush_pending();
+	if (body->slot >= 0) {
+		_write_constant(ctx, body->slot, body->constant_force, body->constant_torque);
+	}
+}
+
+Vector3 BradotPhysicsServerCUDA::body_get_constant_torque(RID p_body) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, Vector3());
+	return body->constant_torque;
+}
+
+// BradotBody3D::set_axis_velocity (bradot_body_3d.h:221-226): the velocity component along the axis is replaced
+void BradotPhysicsServerCUDA::body_set_axis_velocity(RID p_body, const Vector3 &p_axis_velocity) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	Vector3 axis = p_axis_velocity.normalized();
+	Vector3 v = body_get_state(p_body, BODY_STATE_LINEAR_VELOCITY);
+	v -= axis * axis.dot(v);
+	v += p_axis_velocity;
+	body_set_state(p_body, BODY_STATE_LINEAR_VELOCITY, v);
+}
+
+/* callbacks and direct state */
+
+void BradotPhysicsServerCUDA::_body_update_callback_list(Body *p_body) {
+	bool want = p_body->state_sync_callback.is_valid() || p_body->fi_callable.is_valid();
+	if (want && !p_body->has_callbacks) {
+		callback_bodies.push_back(p_body);
+	} else if (!want && p_body->has_callbacks) {
+		callback_bodies.erase(p_body);
+	}
+	p_body->has_callbacks = want;
+}
+
+void BradotPhysicsServerCUDA::body_set_state_sync_callback(RID p_body, const Callable &p_callable) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->state_sync_callback = p_callable;
+	_body_update_callback_list(body);
+}
+
+void BradotPhysicsServerCUDA::body_set_force_integration_callback(RID p_body, const Callable &p_callable, const Variant &p_udata) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->fi_callable = p_callable;
+	body->fi_udata = p_udata;
+	_body_update_callback_list(body);
+}
+
+PhysicsDirectBodyState3D *BradotPhysicsServerCUDA::body_get_direct_state(RID p_body) {
+	// the reference allows this during sync / flush_queries only (bradot_physics_server_3d.cpp:924-940)
+	ERR_FAIL_COND_V_MSG((using_threads && !doing_sync), nullptr, "Body state is inaccessible right now, wait for iteration or physics process notification.");
+	if (!body_owner.owns(p_body)) {
+		return nullptr;
+	}
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, nullptr);
+	if (body->slot < 0 && !body->pending) {
+		return nullptr; // not in a space
+	}
+	if (!body->direct_state) {
+		body->direct_state = memnew(BradotPhysicsDirectBodyStateCUDA);
+		body->direct_state->server = this;
+		body->direct_state->body = p_body;
+	}
+	return body->direct_state;
+}
+
+// BradotBody3D::call_queries (bradot_body_3d.cpp:762-781): the force-integration callback, then the state-sync callback,
+// both handed the body's direct state
+void BradotPhysicsServerCUDA::_body_call_queries(Body *p_body) {
+	Variant direct_state_variant = body_get_direct_state(p_body->self);
+	if (p_body->fi_callable.is_valid()) {
+		const Variant *vp[2] = { &direct_state_variant, &p_body->fi_udata };
+		Callable::CallError ce;
+		int argc = (p_body->fi_udata.get_type() == Variant::NIL) ? 1 : 2;
+		Variant rv;
+		p_body->fi_callable.callp(vp, argc, rv, ce);
+	}
+	if (p_body->state_sync_callback.is_valid()) {
+		p_body->state_sync_callback.call(direct_state_variant);
+	}
+}
+
+#define DIRECT_BODY(m_ret)                                                \
+	BradotPhysicsServerCUDA::Body *b = server->body_owner.get_or_null(body); \
+	ERR_FAIL_NULL_V(b, m_ret);
+
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_total_gravity() const {
+	DIRECT_BODY(Vector3());
+	// default area of the body's space only (areas are a "next" row): gravity vector * gravity * gravity_scale
+	return Vector3(0, -9.80665, 0) * b->gravity_scale;
+}
+real_t BradotPhysicsDirectBodyStateCUDA::get_total_angular_damp() const {
+	DIRECT_BODY(0);
+	return b->ang_damp_replace ? b->ang_damp : 0.1 + b->ang_damp;
+}
+real_t BradotPhysicsDirectBodyStateCUDA::get_total_linear_damp() const {
+	DIRECT_BODY(0);
+	return b->lin_damp_replace ? b->lin_damp : 0.1 + b->lin_damp;
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_center_of_mass() const {
+	DIRECT_BODY(Vector3());
+	Basis iinv;
+	Vector3 com;
+	real_t im = 0;
+	server->_body_mass_world(b, iinv, com, im);
+	return com;
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_center_of_mass_local() const {
+	DIRECT_BODY(Vector3());
+	float m[16];
+	ERR_FAIL_COND_V(b->slot < 0 || bpc_bodies_read(server->ctx, BPC_FIELD_MASS_PROPS, b->slot, 1, m) < 0, Vector3());
+	return Vector3(m[4], m[5], m[6]);
+}
+Basis BradotPhysicsDirectBodyStateCUDA::get_principal_inertia_axes() const {
+	DIRECT_BODY(Basis());
+	float m[16];
+	ERR_FAIL_COND_V(b->slot < 0 || bpc_bodies_read(server->ctx, BPC_FIELD_MASS_PROPS, b->slot, 1, m) < 0, Basis());
+	return get_transform().basis * Basis(m[7], m[8], m[9], m[10], m[11], m[12], m[13], m[14], m[15]);
+}
+real_t BradotPhysicsDirectBodyStateCUDA::get_inverse_mass() const {
+	DIRECT_BODY(0);
+	Basis iinv;
+	Vector3 com;
+	real_t im = 0;
+	server->_body_mass_world(b, iinv, com, im);
+	return im;
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_inverse_inertia() const {
+	DIRECT_BODY(Vector3());
+	float m[16];
+	ERR_FAIL_COND_V(b->slot < 0 || bpc_bodies_read(server->ctx, BPC_FIELD_MASS_PROPS, b->slot, 1, m) < 0, Vector3());
+	return Vector3(m[1], m[2], m[3]);
+}
+Basis BradotPhysicsDirectBodyStateCUDA::get_inverse_inertia_tensor() const {
+	DIRECT_BODY(Basis());
+	Basis iinv;
+	Vector3 com;
+	real_t im = 0;
+	server->_body_mass_world(b, iinv, com, im);
+	return iinv;
+}
+void BradotPhysicsDirectBodyStateCUDA::set_linear_velocity(const Vector3 &p_velocity) {
+	server->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, p_velocity);
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_linear_velocity() const {
+	return server->body_get_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY);
+}
+void BradotPhysicsDirectBodyStateCUDA::set_angular_velocity(const Vector3 &p_velocity) {
+	server->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, p_velocity);
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_angular_velocity() const {
+	return server->body_get_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY);
+}
+void BradotPhysicsDirectBodyStateCUDA::set_transform(const Transform3D &p_transform) {
+	server->body_set_state(body, PhysicsServer3D::BODY_STATE_TRANSFORM, p_transform);
+}
+Transform3D BradotPhysicsDirectBodyStateCUDA::get_transform() const {
+	return server->body_get_state(body, PhysicsServer3D::BODY_STATE_TRANSFORM);
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_velocity_at_local_position(const Vector3 &p_position) const {
+	// BradotBody3D::get_velocity_in_local_point (bradot_body_3d.h:217-219)
+	return get_linear_velocity() + get_angular_velocity().cross(p_position - get_center_of_mass());
+}
+void BradotPhysicsDirectBodyStateCUDA::apply_central_impulse(const Vector3 &p_impulse) { server->body_apply_central_impulse(body, p_impulse); }
+void BradotPhysicsDirectBodyStateCUDA::apply_impulse(const Vector3 &p_impulse, const Vector3 &p_position) { server->body_apply_impulse(body, p_impulse, p_position); }
+void BradotPhysicsDirectBodyStateCUDA::apply_torque_impulse(const Vector3 &p_impulse) { server->body_apply_torque_impulse(body, p_impulse); }
+void BradotPhysicsDirectBodyStateCUDA::apply_central_force(const Vector3 &p_force) { server->body_apply_central_force(body, p_force); }
+void BradotPhysicsDirectBodyStateCUDA::apply_force(const Vector3 &p_force, const Vector3 &p_position) { server->body_apply_force(body, p_force, p_position); }
+void BradotPhysicsDirectBodyStateCUDA::apply_torque(const Vector3 &p_torque) { server->body_apply_torque(body, p_torque); }
+void BradotPhysicsDirectBodyStateCUDA::add_constant_central_force(const Vector3 &p_force) { server->body_add_constant_central_force(body, p_force); }
+void BradotPhysicsDirectBodyStateCUDA::add_constant_force(const Vector3 &p_force, const Vector3 &p_position) { server->body_add_constant_force(body, p_force, p_position); }
+void BradotPhysicsDirectBodyStateCUDA::add_constant_torque(const Vector3 &p_torque) { server->body_add_constant_torque(body, p_torque); }
+void BradotPhysicsDirectBodyStateCUDA::set_constant_force(const Vector3 &p_force) { server->body_set_constant_force(body, p_force); }
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_constant_force() const { return server->body_get_constant_force(body); }
+void BradotPhysicsDirectBodyStateCUDA::set_constant_torque(const Vector3 &p_torque) { server->body_set_constant_torque(body, p_torque); }
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_constant_torque() const { return server->body_get_constant_torque(body); }
+void BradotPhysicsDirectBodyStateCUDA::set_sleep_state(bool p_sleep) { server->body_set_state(body, PhysicsServer3D::BODY_STATE_SLEEPING, p_sleep); }
+bool BradotPhysicsDirectBodyStateCUDA::is_sleeping() const { return server->body_get_state(body, PhysicsServer3D::BODY_STATE_SLEEPING); }
+real_t BradotPhysicsDirectBodyStateCUDA::get_step() const { return server->last_step; }
+PhysicsDirectSpaceState3D *BradotPhysicsDirectBodyStateCUDA::get_space_state() {
+	BradotPhysicsServerCUDA::Body *b = server->body_owner.get_or_null(body);
+	ERR_FAIL_NULL_V(b, nullptr);
+	return server->space_get_direct_state(b->space);
 }
 
 /* JOINTS */
 
 RID BradotPhysicsServerCUDA::joint_create() {
 	Joint *joint = memnew(Joint);
-	return joint_owner.make_rid(joint);
+	RID rid = joint_owner.make_rid(joint);
+	joint->self = rid;
+	return rid;
 }
 
+void BradotPhysicsServerCUDA::_fill_joint_desc(const Joint *p_joint, bpc_joint_desc &r_desc) {
+	const Joint *j = p_joint;
+	const Body *a = body_owner.get_or_null(j->a), *b = body_owner.get_or_null(j->b);
+	r_desc = {};
+	r_desc.type = j->type == JOINT_TYPE_PIN ? BPC_JOINT_PIN : BPC_JOINT_HINGE;
+	r_desc.body_a = a ? a->slot : 0;
+	r_desc.body_b = b ? b->slot : 0;
+	r_desc.flags = (j->disable_collisions ? 1 : 0) | 8; // parameters are always given
+	_xf_to_floats(j->fa, r_desc.frame_a);
+	_xf_to_floats(j->fb, r_desc.frame_b);
+	if (j->type == JOINT_TYPE_PIN) {
+		for (int k = 0; k < 3; k++) {
+			r_desc.params[k] = j->pin_params[k];
+		}
+	} else {
+		for (int k = 0; k < HINGE_JOINT_MAX; k++) {
+			r_desc.params[k] = j->hinge_params[k];
+		}
+		r_desc.flags |= (j->hinge_flags[HINGE_JOINT_FLAG_USE_LIMIT] ? 2 : 0) | (j->hinge_flags[HINGE_JOINT_FLAG_ENABLE_MOTOR] ? 4 : 0);
+	}
+	r_desc.priority = j->priority;
+}
+
+// a parameter, flag or the priority of an uploaded joint changed: rewrite its record
+void BradotPhysicsServerCUDA::_joint_changed(Joint *p_joint) {
+	if (p_joint->handle < 0) {
+		return;
+	}
+	bpc_joint_desc d;
+	_fill_joint_desc(p_joint, d);
+	ERR_FAIL_COND_MSG(bpc_joints_write(ctx, p_joint->handle, 1, &d) < 0, bpc_last_error(ctx));
+}
+
+// joint_clear (bradot_physics_server_3d.cpp:1229-1246): the joint becomes an empty one of no type
 void BradotPhysicsServerCUDA::joint_clear(RID p_joint) {
 	Joint *joint = joint_owner.get_or_null(p_joint);
 	ERR_FAIL_NULL(joint);
-	ERR_FAIL_COND_MSG(joint->handle >= 0, "BradotPhysicsCUDA: joints cannot be cleared once uploaded.");
+	if (joint->handle >= 0) {
+		bpc_joints_destroy(ctx, joint->handle, 1);
+		joint->handle = -1;
+	}
+	if (joint->pending) {
+		pending_joints.erase(joint);
+		joint->pending = false;
+	}
 	joint->type = JOINT_TYPE_MAX;
 }
 
@@ -524,11 +1157,13 @@ void BradotPhysicsServerCUDA::joint_make_pin(RID p_joint, RID p_body_A, const Ve
 	ERR_FAIL_NULL(joint);
 	ERR_FAIL_NULL(body_owner.get_or_null(p_body_A));
 	ERR_FAIL_NULL(body_owner.get_or_null(p_body_B));
+	joint_clear(p_joint);
 	joint->type = JOINT_TYPE_PIN;
 	joint->a = p_body_A;
 	joint->b = p_body_B;
 	joint->fa = Transform3D(Basis(), p_local_A);
 	joint->fb = Transform3D(Basis(), p_local_B);
+	joint->pending = true;
 	pending_joints.push_back(joint);
 }
 
@@ -537,19 +1172,27 @@ void BradotPhysicsServerCUDA::joint_make_hinge(RID p_joint, RID p_body_A, const 
 	ERR_FAIL_NULL(joint);
 	ERR_FAIL_NULL(body_owner.get_or_null(p_body_A));
 	ERR_FAIL_NULL(body_owner.get_or_null(p_body_B));
+	joint_clear(p_joint);
 	joint->type = JOINT_TYPE_HINGE;
 	joint->a = p_body_A;
 	joint->b = p_body_B;
 	joint->fa = p_hinge_A;
 	joint->fb = p_hinge_B;
+	joint->pending = true;
 	pending_joints.push_back(joint);
 }
 
 void BradotPhysicsServerCUDA::joint_disable_collisions_between_bodies(RID p_joint, bool p_disable) {
 	Joint *joint = joint_owner.get_or_null(p_joint);
 	ERR_FAIL_NULL(joint);
-	ERR_FAIL_COND_MSG(joint->handle >= 0, "BradotPhysicsCUDA: set before the first step after creating the joint.");
 	joint->disable_collisions = p_disable;
+	_joint_changed(joint);
+}
+
+bool BradotPhysicsServerCUDA::joint_is_disabled_collisions_between_bodies(RID p_joint) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, true);
+	return joint->disable_collisions;
 }
 
 PhysicsServer3D::JointType BradotPhysicsServerCUDA::joint_get_type(RID p_joint) const {
@@ -558,24 +1201,140 @@ PhysicsServer3D::JointType BradotPhysicsServerCUDA::joint_get_type(RID p_joint) 
 	return joint->type;
 }
 
+void BradotPhysicsServerCUDA::joint_set_solver_priority(RID p_joint, int p_priority) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND_MSG(p_priority < 1 || p_priority > 15, "BradotPhysicsCUDA: joint solver priority must be 1..15.");
+	joint->priority = p_priority;
+	_joint_changed(joint);
+}
+
+int BradotPhysicsServerCUDA::joint_get_solver_priority(RID p_joint) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, 0);
+	return joint->priority;
+}
+
+void BradotPhysicsServerCUDA::pin_joint_set_param(RID p_joint, PinJointParam p_param, real_t p_value) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND(joint->type != JOINT_TYPE_PIN);
+	ERR_FAIL_INDEX((int)p_param, 3);
+	joint->pin_params[p_param] = p_value;
+	_joint_changed(joint);
+}
+
+real_t BradotPhysicsServerCUDA::pin_joint_get_param(RID p_joint, PinJointParam p_param) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, 0);
+	ERR_FAIL_COND_V(joint->type != JOINT_TYPE_PIN, 0);
+	ERR_FAIL_INDEX_V((int)p_param, 3, 0);
+	return joint->pin_params[p_param];
+}
+
+void BradotPhysicsServerCUDA::pin_joint_set_local_a(RID p_joint, const Vector3 &p_A) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND(joint->type != JOINT_TYPE_PIN);
+	joint->fa.origin = p_A;
+	_joint_changed(joint);
+}
+Vector3 BradotPhysicsServerCUDA::pin_joint_get_local_a(RID p_joint) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, Vector3());
+	return joint->fa.origin;
+}
+void BradotPhysicsServerCUDA::pin_joint_set_local_b(RID p_joint, const Vector3 &p_B) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND(joint->type != JOINT_TYPE_PIN);
+	joint->fb.origin = p_B;
+	_joint_changed(joint);
+}
+Vector3 BradotPhysicsServerCUDA::pin_joint_get_local_b(RID p_joint) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, Vector3());
+	return joint->fb.origin;
+}
+
+void BradotPhysicsServerCUDA::hinge_joint_set_param(RID p_joint, HingeJointParam p_param, real_t p_value) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND(joint->type != JOINT_TYPE_HINGE);
+	ERR_FAIL_INDEX((int)p_param, (int)HINGE_JOINT_MAX);
+	joint->hinge_params[p_param] = p_value;
+	_joint_changed(joint);
+}
+
+real_t BradotPhysicsServerCUDA::hinge_joint_get_param(RID p_joint, HingeJointParam p_param) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, 0);
+	ERR_FAIL_COND_V(joint->type != JOINT_TYPE_HINGE, 0);
+	ERR_FAIL_INDEX_V((int)p_param, (int)HINGE_JOINT_MAX, 0);
+	return joint->hinge_params[p_param];
+}
+
+void BradotPhysicsServerCUDA::hinge_joint_set_flag(RID p_joint, HingeJointFlag p_flag, bool p_enabled) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND(joint->type != JOINT_TYPE_HINGE);
+	ERR_FAIL_INDEX((int)p_flag, (int)HINGE_JOINT_FLAG_MAX);
+	joint->hinge_flags[p_flag] = p_enabled;
+	_joint_changed(joint);
+}
+
+bool BradotPhysicsServerCUDA::hinge_joint_get_flag(RID p_joint, HingeJointFlag p_flag) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, false);
+	ERR_FAIL_COND_V(joint->type != JOINT_TYPE_HINGE, false);
+	ERR_FAIL_INDEX_V((int)p_flag, (int)HINGE_JOINT_FLAG_MAX, false);
+	return joint->hinge_flags[p_flag];
+}
+
 /* LIFECYCLE */
 
+// free(RID) of any kind (bradot_physics_server_3d.cpp:1557-1622).  A body leaves the GPU side with its slot (reused by the
+// next upload); freeing a space frees what is in it.
 void BradotPhysicsServerCUDA::free(RID p_rid) {
-	// GPU slots are not recycled in this version; host records are released like the reference does
-	// (modules/bradot_physics_3d/bradot_physics_server_3d.cpp:1557-1622).
 	if (shape_owner.owns(p_rid)) {
 		Shape *s = shape_owner.get_or_null(p_rid);
 		shape_owner.free(p_rid);
 		memdelete(s);
 	} else if (body_owner.owns(p_rid)) {
 		Body *b = body_owner.get_or_null(p_rid);
-		ERR_FAIL_COND_MSG(b->slot >= 0, "BradotPhysicsCUDA: removing an uploaded body is not supported yet.");
-		pending_bodies.erase(b);
-		pushed_bodies.erase(b);
+		_body_leave_space(b);
+		if (b->pushed) {
+			pushed_bodies.erase(b);
+		}
+		if (b->has_callbacks) {
+			callback_bodies.erase(b);
+		}
+		// joints of the body stay valid RIDs of no effect, as in the reference until they are freed themselves
+		List<RID> joints;
+		joint_owner.get_owned_list(&joints);
+		for (const RID &jr : joints) {
+			Joint *j = joint_owner.get_or_null(jr);
+			if (j && (j->a == p_rid || j->b == p_rid)) {
+				joint_clear(jr);
+			}
+		}
+		if (b->direct_state) {
+			memdelete(b->direct_state);
+		}
 		body_owner.free(p_rid);
 		memdelete(b);
 	} else if (space_owner.owns(p_rid)) {
 		Space *s = space_owner.get_or_null(p_rid);
+		List<RID> bodies;
+		body_owner.get_owned_list(&bodies);
+		for (const RID &br : bodies) {
+			Body *b = body_owner.get_or_null(br);
+			if (b && b->space == p_rid) { // the body outlives its space, outside of any (co->set_space(nullptr))
+				_body_leave_space(b);
+				b->space = RID();
+			}
+		}
+		bpc_space_destroy(ctx, s->handle);
 		if (s->direct_state) {
 			memdelete(s->direct_state);
 		}
@@ -583,7 +1342,7 @@ void BradotPhysicsServerCUDA::free(RID p_rid) {
 		memdelete(s);
 	} else if (joint_owner.owns(p_rid)) {
 		Joint *j = joint_owner.get_or_null(p_rid);
-		pending_joints.erase(j);
+		joint_clear(p_rid);
 		joint_owner.free(p_rid);
 		memdelete(j);
 	} else {
@@ -600,109 +1359,110 @@ void BradotPhysicsServerCUDA::init() {
 	ERR_FAIL_NULL_MSG(ctx, "BradotPhysicsCUDA: no usable CUDA device (this backend has no CPU fallback).");
 }
 
-// Upload everything created since the last tick in bulk.
+// Everything created or re-described since the last tick goes to the GPU in bulk: new bodies in one bpc_bodies_create_slots
+// (freed slots first), changed ones in one bpc_bodies_update, new joints in one bpc_joints_create.
 void BradotPhysicsServerCUDA::_flush_pending() {
 	if (!pending_bodies.is_empty()) {
 		LocalVector<bpc_body_desc> descs;
-		LocalVector<Body *> uploaded;
+		LocalVector<Body *> uploaded, waiting;
 		for (Body *b : pending_bodies) {
 			Shape *shape = shape_owner.get_or_null(b->shape);
 			Space *space = space_owner.get_or_null(b->space);
-			if (!shape || !space) {
-				continue; // shapeless bodies (the reference's static global body) take no part in the step
-			}
-			int sh = _shape_handle(shape);
-			if (sh < 0) {
+			if (!space) {
+				b->pending = false;
 				continue;
 			}
-			bpc_body_desc d = {};
-			d.space = space->handle;
-			d.mode = (uint32_t)b->mode;
-			d.shape = sh;
-			d.flags = (b->can_sleep ? 1 : 0) | (b->ccd ? 2 : 0);
-			_xf_to_floats(b->xf, d.xf);
-			_xf_to_floats(b->shape_xf, d.shape_xf);
-			d.linvel[0] = b->linvel.x; d.linvel[1] = b->linvel.y; d.linvel[2] = b->linvel.z;
-			d.angvel[0] = b->angvel.x; d.angvel[1] = b->angvel.y; d.angvel[2] = b->angvel.z;
-			d.mass = b->mass; d.friction = b->friction; d.bounce = b->bounce; d.gravity_scale = b->gravity_scale;
-			d.lin_damp = b->lin_damp; d.ang_damp = b->ang_damp; d.layer = b->layer; d.mask = b->mask;
+			if (!shape || _shape_handle(shape) < 0) {
+				waiting.push_back(b); // shapeless bodies (the reference's static global body) take no part in the step
+				continue;
+			}
+			bpc_body_desc d;
+			_fill_desc(b, d);
 			descs.push_back(d);
 			uploaded.push_back(b);
 		}
-		if (!descs.is_empty()) {
-			int first = bpc_bodies_create(ctx, descs.ptr(), descs.size());
-			ERR_FAIL_COND_MSG(first < 0, bpc_last_error(ctx));
-			for (uint32_t i = 0; i < uploaded.size(); i++) {
-				uploaded[i]->slot = first + i;
-				if (body_of_slot.size() <= (uint32_t)(first + i)) {
-					body_of_slot.resize(first + i + 1);
-				}
-				body_of_slot[first + i] = uploaded[i];
-			}
-		}
 		pending_bodies.clear();
+		for (Body *b : waiting) {
+			pending_bodies.push_back(b);
+		}
+		if (!descs.is_empty()) {
+			LocalVector<int32_t> slots;
+			slots.resize(descs.size());
+			ERR_FAIL_COND_MSG(bpc_bodies_create_slots(ctx, descs.ptr(), descs.size(), slots.ptr()) < 0, bpc_last_error(ctx));
+			for (uint32_t i = 0; i < uploaded.size(); i++) {
+				Body *b = uploaded[i];
+				b->slot = slots[i];
+				b->pending = false;
+				if (body_of_slot.size() <= (uint32_t)slots[i]) {
+					body_of_slot.resize(slots[i] + 1);
+				}
+				body_of_slot[slots[i]] = b;
+				if (b->constant_force != Vector3() || b->constant_torque != Vector3()) {
+					_write_constant(ctx, b->slot, b->constant_force, b->constant_torque);
+				}
+			}
+			// exceptions named before both bodies were in a space
+			for (Body *b : uploaded) {
+				for (const RID &r : b->exceptions) {
+					Body *o = body_owner.get_or_null(r);
+					if (o && o->slot >= 0) {
+						bpc_bodies_set_exception(ctx, b->slot, o->slot, 1);
+					}
+				}
+			}
+			state_cache_valid = false;
+		}
+	}
+	if (!dirty_bodies.is_empty()) {
+		LocalVector<bpc_body_desc> descs;
+		LocalVector<int32_t> slots;
+		for (Body *b : dirty_bodies) {
+			b->dirty = false;
+			if (b->slot < 0 || !shape_owner.get_or_null(b->shape)) {
+				continue;
+			}
+			bpc_body_desc d;
+			_fill_desc(b, d);
+			descs.push_back(d);
+			slots.push_back(b->slot);
+		}
+		dirty_bodies.clear();
+		if (!descs.is_empty()) {
+			ERR_FAIL_COND_MSG(bpc_bodies_update(ctx, slots.ptr(), slots.size(), descs.ptr(), 1) < 0, bpc_last_error(ctx));
+		}
 	}
 	if (!pending_joints.is_empty()) {
 		LocalVector<bpc_joint_desc> descs;
-		LocalVector<Joint *> uploaded;
+		LocalVector<Joint *> uploaded, waiting;
 		for (Joint *j : pending_joints) {
 			Body *a = body_owner.get_or_null(j->a);
 			Body *b = body_owner.get_or_null(j->b);
-			if (!a || !b || a->slot < 0 || b->slot < 0 || j->type == JOINT_TYPE_MAX) {
+			if (!a || !b || j->type == JOINT_TYPE_MAX) {
+				j->pending = false;
 				continue;
 			}
-			bpc_joint_desc d = {};
-			d.type = j->type == JOINT_TYPE_PIN ? BPC_JOINT_PIN : BPC_JOINT_HINGE;
-			d.body_a = a->slot;
-			d.body_b = b->slot;
-			d.flags = j->disable_collisions ? 1 : 0;
-			_xf_to_floats(j->fa, d.frame_a);
-			_xf_to_floats(j->fb, d.frame_b);
+			if (a->slot < 0 || b->slot < 0) {
+				waiting.push_back(j); // one of its bodies is not in a space yet
+				continue;
+			}
+			bpc_joint_desc d;
+			_fill_joint_desc(j, d);
 			descs.push_back(d);
 			uploaded.push_back(j);
+		}
+		pending_joints.clear();
+		for (Joint *j : waiting) {
+			pending_joints.push_back(j);
 		}
 		if (!descs.is_empty()) {
 			int first = bpc_joints_create(ctx, descs.ptr(), descs.size());
 			ERR_FAIL_COND_MSG(first < 0, bpc_last_error(ctx));
 			for (uint32_t i = 0; i < uploaded.size(); i++) {
 				uploaded[i]->handle = first + i;
+				uploaded[i]->pending = false;
 			}
 		}
-		pending_joints.clear();
 	}
-}
-
-void BradotPhysicsServerCUDA::body_set_enable_continuous_collision_detection(RID p_body, bool p_enable) {
-	Body *body = body_owner.get_or_null(p_body);
-	ERR_FAIL_NULL(body);
-	ERR_FAIL_COND_MSG(body->slot >= 0, "BradotPhysicsCUDA: continuous collision detection is fixed once the body is in a space (bulk upload).");
-	body->ccd = p_enable;
-}
-
-bool BradotPhysicsServerCUDA::body_is_continuous_collision_detection_enabled(RID p_body) const {
-	const Body *body = body_owner.get_or_null(p_body);
-	ERR_FAIL_NULL_V(body, false);
-	return body->ccd;
-}
-
-// body_apply_central_force / body_apply_torque (bradot_physics_server_3d.cpp:859-897): accumulated on the host, handed to
-// the GPU as one BPC_FIELD_APPLIED_FORCE row per pushed body before the step (a non-zero row wakes the body there)
-void BradotPhysicsServerCUDA::body_apply_central_force(RID p_body, const Vector3 &p_force) {
-	Body *body = body_owner.get_or_null(p_body);
-	ERR_FAIL_NULL(body);
-	if (body->applied_force == Vector3() && body->applied_torque == Vector3()) {
-		pushed_bodies.push_back(body);
-	}
-	body->applied_force += p_force;
-}
-
-void BradotPhysicsServerCUDA::body_apply_torque(RID p_body, const Vector3 &p_torque) {
-	Body *body = body_owner.get_or_null(p_body);
-	ERR_FAIL_NULL(body);
-	if (body->applied_force == Vector3() && body->applied_torque == Vector3()) {
-		pushed_bodies.push_back(body);
-	}
-	body->applied_torque += p_torque;
 }
 
 void BradotPhysicsServerCUDA::step(real_t p_step) {
@@ -710,35 +1470,85 @@ void BradotPhysicsServerCUDA::step(real_t p_step) {
 		return;
 	}
 	_flush_pending();
-	for (Body *b : pushed_bodies) {
-		if (b->slot >= 0) {
-			float f[6] = { (float)b->applied_force.x, (float)b->applied_force.y, (float)b->applied_force.z,
-				(float)b->applied_torque.x, (float)b->applied_torque.y, (float)b->applied_torque.z };
-			bpc_bodies_write(ctx, BPC_FIELD_APPLIED_FORCE, b->slot, 1, f);
+	if (!pushed_bodies.is_empty()) { // ONE scattered write for every pushed body
+		LocalVector<int32_t> slots;
+		LocalVector<float> rows;
+		for (Body *b : pushed_bodies) {
+			if (b->slot >= 0) {
+				slots.push_back(b->slot);
+				rows.push_back(b->applied_force.x); rows.push_back(b->applied_force.y); rows.push_back(b->applied_force.z);
+				rows.push_back(b->applied_torque.x); rows.push_back(b->applied_torque.y); rows.push_back(b->applied_torque.z);
+			}
+			b->applied_force = Vector3();
+			b->applied_torque = Vector3();
+			b->pushed = false;
 		}
-		b->applied_force = Vector3();
-		b->applied_torque = Vector3();
+		pushed_bodies.clear();
+		if (!slots.is_empty()) {
+			ERR_FAIL_COND_MSG(bpc_bodies_write_slots(ctx, BPC_FIELD_APPLIED_FORCE, slots.ptr(), slots.size(), rows.ptr()) < 0, bpc_last_error(ctx));
+		}
 	}
-	pushed_bodies.clear();
+	last_step = p_step;
+	stepped_since_flush = true;
+	state_cache_valid = false;
 	ERR_FAIL_COND_MSG(bpc_step(ctx, p_step) < 0, bpc_last_error(ctx));
 }
 
 void BradotPhysicsServerCUDA::sync() {
+	doing_sync = true;
 	if (ctx) {
 		bpc_synchronize(ctx);
 	}
 }
 
+// BradotSpace3D::call_queries (bradot_space_3d.cpp:1164-1176): every body that was integrated in the last step and has a
+// state-sync or force-integration callback gets it, with its direct state.  The whole body state comes back in ONE copy
+// (19 floats per slot); "was integrated" = active before or after the step (a body that fell asleep in this very step was
+// still moved by it and reports its last transform, as in the reference, where integrate_velocities queues the callback).
 void BradotPhysicsServerCUDA::flush_queries() {
 	if (!active || !ctx) {
 		return;
 	}
 	flushing_queries = true;
+	_flush_pending();
 	bpc_get_stats(ctx, &last_stats);
+	int n = bpc_body_count(ctx);
+	if (n > 0 && !callback_bodies.is_empty() && stepped_since_flush) { // no step, nothing was integrated, nobody is told
+		stepped_since_flush = false;
+		state_cache.resize((uint32_t)n * 19);
+		if (bpc_bodies_read_state(ctx, 0, n, state_cache.ptr()) < 0) {
+			flushing_queries = false;
+			ERR_FAIL_MSG(bpc_last_error(ctx));
+		}
+		state_cache_valid = true;
+		uint32_t old = was_active.size();
+		was_active.resize(n);
+		for (uint32_t i = old; i < (uint32_t)n; i++) {
+			was_active[i] = 1; // a new body counts as active before its first step
+		}
+		// the callbacks may create, free or re-describe bodies: walk a copy
+		LocalVector<Body *> todo;
+		for (Body *b : callback_bodies) {
+			// (a static body is never integrated: integrate_velocities returns before queueing it, bradot_body_3d.cpp:675-683)
+			if (b->slot >= 0 && b->slot < n && b->mode != BODY_MODE_STATIC && (state_cache[b->slot * 19 + 18] != 0.f || was_active[b->slot])) {
+				todo.push_back(b);
+			}
+		}
+		for (int i = 0; i < n; i++) {
+			was_active[i] = state_cache[i * 19 + 18] != 0.f;
+		}
+		for (Body *b : todo) {
+			if (callback_bodies.has(b)) {
+				_body_call_queries(b);
+			}
+		}
+	}
 	flushing_queries = false;
 }
 
-void BradotPhysicsServerCUDA::end_sync() {}
+void BradotPhysicsServerCUDA::end_sync() {
+	doing_sync = false;
+}
 
 void BradotPhysicsServerCUDA::finish() {
 	if (ctx) {
@@ -764,7 +1574,8 @@ int BradotPhysicsServerCUDA::get_process_info(ProcessInfo p_info) {
 	return 0;
 }
 
-BradotPhysicsServerCUDA::BradotPhysicsServerCUDA(bool p_using_threads) {}
+BradotPhysicsServerCUDA::BradotPhysicsServerCUDA(bool p_using_threads) :
+		using_threads(p_using_threads) {}
 
 BradotPhysicsServerCUDA::~BradotPhysicsServerCUDA() {
 	finish();

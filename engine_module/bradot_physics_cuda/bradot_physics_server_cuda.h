@@ -3,10 +3,13 @@
 // register_types.cpp registers it as "BradotPhysicsCUDA" with PhysicsServer3DManager
 // (servers/physics_server_3d.cpp:1170-1175), selectable through physics/3d/physics_engine.
 //
-// Implemented by hand: what the step needs (spaces, world-boundary / sphere / box / capsule / convex shapes,
-// rigid and static bodies with one shape, pin and hinge joints, state access, step, stats).  Every other pure
-// virtual of the interface gets a generated default override (engine_module/gen_stubs.py) that logs once and
-// returns the type's default, which is how the reference answers an invalid RID.
+// Implemented by hand: what a scene of RigidBody3D / StaticBody3D nodes needs -- spaces (create, activate, parameters, free),
+// world-boundary / sphere / box / capsule / convex shapes, bodies with one shape (every setter also after the body is in a
+// space; state-sync and force-integration callbacks; PhysicsDirectBodyState3D; impulses, forces, constant forces; axis
+// locks; collision exceptions; free), pin and hinge joints with their parameters, flags and solver priority, step, stats,
+// PhysicsDirectSpaceState3D queries.  Every other pure virtual of the interface gets a generated default override
+// (engine_module/gen_stubs.py) that logs once and returns the type's default, which is how the reference answers an
+// invalid RID.
 #ifndef BRADOT_PHYSICS_SERVER_CUDA_H
 #define BRADOT_PHYSICS_SERVER_CUDA_H
 
@@ -40,9 +43,67 @@ public:
 	virtual Vector3 get_closest_point_to_object_volume(RID p_object, const Vector3 p_point) const override { BPC_UNSUPPORTED("get_closest_point_to_object_volume"); return p_point; }
 };
 
+// PhysicsDirectBodyState3D of one body (servers/physics_server_3d.h:46-115; reference implementation
+// modules/bradot_physics_3d/bradot_body_direct_state_3d.cpp).  Getters answer from the state the server read back in bulk at
+// the start of flush_queries(); setters go through the server's own entry points (body_set_state, body_apply_*).
+class BradotPhysicsDirectBodyStateCUDA : public PhysicsDirectBodyState3D {
+	BRCLASS(BradotPhysicsDirectBodyStateCUDA, PhysicsDirectBodyState3D);
+
+public:
+	BradotPhysicsServerCUDA *server = nullptr;
+	RID body;
+
+	virtual Vector3 get_total_gravity() const override;
+	virtual real_t get_total_angular_damp() const override;
+	virtual real_t get_total_linear_damp() const override;
+	virtual Vector3 get_center_of_mass() const override;
+	virtual Vector3 get_center_of_mass_local() const override;
+	virtual Basis get_principal_inertia_axes() const override;
+	virtual real_t get_inverse_mass() const override;
+	virtual Vector3 get_inverse_inertia() const override;
+	virtual Basis get_inverse_inertia_tensor() const override;
+	virtual void set_linear_velocity(const Vector3 &p_velocity) override;
+	virtual Vector3 get_linear_velocity() const override;
+	virtual void set_angular_velocity(const Vector3 &p_velocity) override;
+	virtual Vector3 get_angular_velocity() const override;
+	virtual void set_transform(const Transform3D &p_transform) override;
+	virtual Transform3D get_transform() const override;
+	virtual Vector3 get_velocity_at_local_position(const Vector3 &p_position) const override;
+	virtual void apply_central_impulse(const Vector3 &p_impulse) override;
+	virtual void apply_impulse(const Vector3 &p_impulse, const Vector3 &p_position = Vector3()) override;
+	virtual void apply_torque_impulse(const Vector3 &p_impulse) override;
+	virtual void apply_central_force(const Vector3 &p_force) override;
+	virtual void apply_force(const Vector3 &p_force, const Vector3 &p_position = Vector3()) override;
+	virtual void apply_torque(const Vector3 &p_torque) override;
+	virtual void add_constant_central_force(const Vector3 &p_force) override;
+	virtual void add_constant_force(const Vector3 &p_force, const Vector3 &p_position = Vector3()) override;
+	virtual void add_constant_torque(const Vector3 &p_torque) override;
+	virtual void set_constant_force(const Vector3 &p_force) override;
+	virtual Vector3 get_constant_force() const override;
+	virtual void set_constant_torque(const Vector3 &p_torque) override;
+	virtual Vector3 get_constant_torque() const override;
+	virtual void set_sleep_state(bool p_sleep) override;
+	virtual bool is_sleeping() const override;
+	// contact reporting is a "next" row: a body reports no contacts
+	virtual int get_contact_count() const override { return 0; }
+	virtual Vector3 get_contact_local_position(int p_contact_idx) const override { return Vector3(); }
+	virtual Vector3 get_contact_local_normal(int p_contact_idx) const override { return Vector3(); }
+	virtual Vector3 get_contact_impulse(int p_contact_idx) const override { return Vector3(); }
+	virtual int get_contact_local_shape(int p_contact_idx) const override { return 0; }
+	virtual Vector3 get_contact_local_velocity_at_position(int p_contact_idx) const override { return Vector3(); }
+	virtual RID get_contact_collider(int p_contact_idx) const override { return RID(); }
+	virtual Vector3 get_contact_collider_position(int p_contact_idx) const override { return Vector3(); }
+	virtual ObjectID get_contact_collider_id(int p_contact_idx) const override { return ObjectID(); }
+	virtual int get_contact_collider_shape(int p_contact_idx) const override { return 0; }
+	virtual Vector3 get_contact_collider_velocity_at_position(int p_contact_idx) const override { return Vector3(); }
+	virtual real_t get_step() const override;
+	virtual PhysicsDirectSpaceState3D *get_space_state() override;
+};
+
 class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	BRCLASS(BradotPhysicsServerCUDA, PhysicsServer3D);
 	friend class BradotPhysicsDirectSpaceStateCUDA;
+	friend class BradotPhysicsDirectBodyStateCUDA;
 
 	struct Shape {
 		ShapeType type = SHAPE_SPHERE;
@@ -65,14 +126,34 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		uint32_t layer = 1, mask = 1;
 		bool can_sleep = true;
 		bool ccd = false;
-		Vector3 applied_force, applied_torque; // accumulated by body_apply_*, handed over at the next step
+		bool omit_force_integration = false;
+		bool lin_damp_replace = false, ang_damp_replace = false;
+		uint32_t locked_axis = 0;
+		ObjectID instance_id;
+		Vector3 applied_force, applied_torque; // accumulated by body_apply_*, handed over in one write before the next step
+		Vector3 constant_force, constant_torque;
+		bool pushed = false;      // in pushed_bodies
+		bool dirty = false;       // described anew since the upload (mode, parameters, layers, shape ...): in dirty_bodies
+		bool pending = false;     // in pending_bodies
+		bool has_callbacks = false; // in callback_bodies
+		Callable state_sync_callback;
+		Callable fi_callable;
+		Variant fi_udata;
+		BradotPhysicsDirectBodyStateCUDA *direct_state = nullptr;
+		LocalVector<RID> exceptions;
 		int slot = -1; // bpc body index once uploaded
 	};
 	struct Joint {
 		JointType type = JOINT_TYPE_MAX;
-		RID a, b;
+		RID self, a, b;
 		Transform3D fa, fb;
 		bool disable_collisions = false;
+		int priority = 1;
+		real_t pin_params[3] = { 0.3, 1.0, 0.0 };
+		// HingeJointParam order; defaults of modules/bradot_physics_3d/joints/bradot_hinge_joint_3d.h:73-88
+		real_t hinge_params[HINGE_JOINT_MAX] = { 0.3, -Math_PI, Math_PI, 0.3, 0.9, 1.0, 0.0, 0.0 };
+		bool hinge_flags[HINGE_JOINT_FLAG_MAX] = { false, false };
+		bool pending = false;
 		int handle = -1;
 	};
 
@@ -84,14 +165,35 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	bpc_context *ctx = nullptr;
 	bool active = true;
 	bool flushing_queries = false;
+	bool doing_sync = false;
+	bool using_threads = false;
+	bool stepped_since_flush = false;
+	real_t last_step = 0.0;
 	LocalVector<Body *> pending_bodies;
-	LocalVector<Body *> body_of_slot; // bpc body index -> body (what a query result is mapped back through)
+	LocalVector<Body *> dirty_bodies;
+	LocalVector<Body *> body_of_slot; // bpc body index -> body (what a query result is mapped back through); nullptr = free slot
 	LocalVector<Joint *> pending_joints;
-	LocalVector<Body *> pushed_bodies; // bodies with a non-zero applied force / torque for the next step
+	LocalVector<Body *> pushed_bodies;   // bodies with a non-zero applied force / torque for the next step
+	LocalVector<Body *> callback_bodies; // bodies with a state-sync or force-integration callback
+	// body state of the last tick, read back in ONE copy at the start of flush_queries(): 19 floats per slot
+	// (transform, linear velocity, angular velocity, active) -- what the callbacks and the direct state answer from
+	LocalVector<float> state_cache;
+	LocalVector<uint8_t> was_active; // active flag per slot one tick earlier
+	bool state_cache_valid = false;
 	bpc_stats last_stats = {};
 
 	int _shape_handle(Shape *p_shape);
 	void _flush_pending();
+	void _fill_desc(const Body *p_body, bpc_body_desc &r_desc);
+	void _fill_joint_desc(const Joint *p_joint, bpc_joint_desc &r_desc);
+	void _body_changed(Body *p_body);
+	void _joint_changed(Joint *p_joint);
+	void _body_leave_space(Body *p_body);
+	void _body_update_callback_list(Body *p_body);
+	void _body_call_queries(Body *p_body);
+	void _body_push(Body *p_body);
+	const float *_body_cached_state(const Body *p_body);
+	bool _body_mass_world(const Body *p_body, Basis &r_iinv, Vector3 &r_com, real_t &r_inv_mass) const;
 
 protected:
 	static void _bind_methods() {}
@@ -120,7 +222,16 @@ public:
 	virtual void body_set_mode(RID p_body, BodyMode p_mode) override;
 	virtual BodyMode body_get_mode(RID p_body) const override;
 	virtual void body_add_shape(RID p_body, RID p_shape, const Transform3D &p_transform = Transform3D(), bool p_disabled = false) override;
+	virtual void body_set_shape(RID p_body, int p_shape_idx, RID p_shape) override;
+	virtual void body_set_shape_transform(RID p_body, int p_shape_idx, const Transform3D &p_transform) override;
+	virtual RID body_get_shape(RID p_body, int p_shape_idx) const override;
+	virtual Transform3D body_get_shape_transform(RID p_body, int p_shape_idx) const override;
+	virtual void body_remove_shape(RID p_body, int p_shape_idx) override;
+	virtual void body_clear_shapes(RID p_body) override;
 	virtual int body_get_shape_count(RID p_body) const override;
+	virtual void body_attach_object_instance_id(RID p_body, ObjectID p_id) override;
+	virtual ObjectID body_get_object_instance_id(RID p_body) const override;
+	virtual void body_reset_mass_properties(RID p_body) override {}
 	virtual void body_set_collision_layer(RID p_body, uint32_t p_layer) override;
 	virtual uint32_t body_get_collision_layer(RID p_body) const override;
 	virtual void body_set_collision_mask(RID p_body, uint32_t p_mask) override;
@@ -131,15 +242,50 @@ public:
 	virtual Variant body_get_state(RID p_body, BodyState p_state) const override;
 	virtual void body_set_enable_continuous_collision_detection(RID p_body, bool p_enable) override;
 	virtual bool body_is_continuous_collision_detection_enabled(RID p_body) const override;
+	virtual void body_apply_central_impulse(RID p_body, const Vector3 &p_impulse) override;
+	virtual void body_apply_impulse(RID p_body, const Vector3 &p_impulse, const Vector3 &p_position = Vector3()) override;
+	virtual void body_apply_torque_impulse(RID p_body, const Vector3 &p_impulse) override;
 	virtual void body_apply_central_force(RID p_body, const Vector3 &p_force) override;
+	virtual void body_apply_force(RID p_body, const Vector3 &p_force, const Vector3 &p_position = Vector3()) override;
 	virtual void body_apply_torque(RID p_body, const Vector3 &p_torque) override;
+	virtual void body_add_constant_central_force(RID p_body, const Vector3 &p_force) override;
+	virtual void body_add_constant_force(RID p_body, const Vector3 &p_force, const Vector3 &p_position = Vector3()) override;
+	virtual void body_add_constant_torque(RID p_body, const Vector3 &p_torque) override;
+	virtual void body_set_constant_force(RID p_body, const Vector3 &p_force) override;
+	virtual Vector3 body_get_constant_force(RID p_body) const override;
+	virtual void body_set_constant_torque(RID p_body, const Vector3 &p_torque) override;
+	virtual Vector3 body_get_constant_torque(RID p_body) const override;
+	virtual void body_set_axis_velocity(RID p_body, const Vector3 &p_axis_velocity) override;
+	virtual void body_set_axis_lock(RID p_body, BodyAxis p_axis, bool p_lock) override;
+	virtual bool body_is_axis_locked(RID p_body, BodyAxis p_axis) const override;
+	virtual void body_add_collision_exception(RID p_body, RID p_body_b) override;
+	virtual void body_remove_collision_exception(RID p_body, RID p_body_b) override;
+	virtual void body_get_collision_exceptions(RID p_body, List<RID> *p_exceptions) override;
+	virtual void body_set_omit_force_integration(RID p_body, bool p_omit) override;
+	virtual bool body_is_omitting_force_integration(RID p_body) const override;
+	virtual void body_set_state_sync_callback(RID p_body, const Callable &p_callable) override;
+	virtual void body_set_force_integration_callback(RID p_body, const Callable &p_callable, const Variant &p_udata = Variant()) override;
+	virtual PhysicsDirectBodyState3D *body_get_direct_state(RID p_body) override;
 	// joints
 	virtual RID joint_create() override;
 	virtual void joint_clear(RID p_joint) override;
 	virtual void joint_make_pin(RID p_joint, RID p_body_A, const Vector3 &p_local_A, RID p_body_B, const Vector3 &p_local_B) override;
 	virtual void joint_make_hinge(RID p_joint, RID p_body_A, const Transform3D &p_hinge_A, RID p_body_B, const Transform3D &p_hinge_B) override;
 	virtual void joint_disable_collisions_between_bodies(RID p_joint, bool p_disable) override;
+	virtual bool joint_is_disabled_collisions_between_bodies(RID p_joint) const override;
 	virtual JointType joint_get_type(RID p_joint) const override;
+	virtual void joint_set_solver_priority(RID p_joint, int p_priority) override;
+	virtual int joint_get_solver_priority(RID p_joint) const override;
+	virtual void pin_joint_set_param(RID p_joint, PinJointParam p_param, real_t p_value) override;
+	virtual real_t pin_joint_get_param(RID p_joint, PinJointParam p_param) const override;
+	virtual void pin_joint_set_local_a(RID p_joint, const Vector3 &p_A) override;
+	virtual Vector3 pin_joint_get_local_a(RID p_joint) const override;
+	virtual void pin_joint_set_local_b(RID p_joint, const Vector3 &p_B) override;
+	virtual Vector3 pin_joint_get_local_b(RID p_joint) const override;
+	virtual void hinge_joint_set_param(RID p_joint, HingeJointParam p_param, real_t p_value) override;
+	virtual real_t hinge_joint_get_param(RID p_joint, HingeJointParam p_param) const override;
+	virtual void hinge_joint_set_flag(RID p_joint, HingeJointFlag p_flag, bool p_enabled) override;
+	virtual bool hinge_joint_get_flag(RID p_joint, HingeJointFlag p_flag) const override;
 	// lifecycle
 	virtual void free(RID p_rid) override;
 	virtual void set_active(bool p_active) override;

@@ -13,14 +13,14 @@ ROOT = os.path.dirname(HERE)
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import build_ref  # noqa: E402  (compiler flags / include paths of the engine build)
 
-MINE = ["world_boundary_shape_create", "sphere_shape_create", "box_shape_create", "capsule_shape_create", "convex_polygon_shape_create",
-        "shape_set_data", "shape_get_type", "shape_get_data", "space_create", "space_set_active", "space_is_active", "space_set_param",
-        "space_get_param", "space_get_direct_state", "body_create", "body_set_space", "body_get_space", "body_set_mode", "body_get_mode", "body_add_shape",
-        "body_get_shape_count", "body_set_collision_layer", "body_get_collision_layer", "body_set_collision_mask", "body_get_collision_mask",
-        "body_set_param", "body_get_param", "body_set_state", "body_get_state", "body_set_enable_continuous_collision_detection",
-        "body_is_continuous_collision_detection_enabled", "body_apply_central_force", "body_apply_torque", "joint_create", "joint_clear", "joint_make_pin",
-        "joint_make_hinge", "joint_disable_collisions_between_bodies", "joint_get_type", "free", "set_active", "init", "step", "sync",
-        "flush_queries", "end_sync", "finish", "is_flushing_queries", "get_process_info"]
+def hand_written():
+    """Names of the PhysicsServer3D virtuals the module implements by hand: every `virtual ... name(...) override` declared
+    in the server class of bradot_physics_server_cuda.h (the rest get generated defaults)."""
+    import re
+    text = open(os.path.join(HERE, "bradot_physics_cuda", "bradot_physics_server_cuda.h")).read()
+    cls = text[text.index("class BradotPhysicsServerCUDA : public PhysicsServer3D"):]
+    cls = cls[:cls.index('#include "bradot_physics_server_cuda_stubs.gen.inc"')]
+    return sorted(set(re.findall(r"virtual\s+[^;{}]*?\b(\w+)\s*\([^;{}]*\)\s*(?:const\s*)?override", cls)))
 
 
 def build():
@@ -30,7 +30,7 @@ def build():
     out = os.path.join(HERE, "_build")
     gen = os.path.join(out, "gen")
     os.makedirs(gen, exist_ok=True)
-    subprocess.run([sys.executable, os.path.join(HERE, "gen_stubs.py"), build_ref.REF, os.path.join(gen, "bradot_physics_server_cuda_stubs.gen.inc")] + MINE, check=True)
+    subprocess.run([sys.executable, os.path.join(HERE, "gen_stubs.py"), build_ref.REF, os.path.join(gen, "bradot_physics_server_cuda_stubs.gen.inc")] + hand_written(), check=True)
     lib_dir = os.path.join(ROOT, "bradot_b200")
     srcs = [os.path.join(HERE, "bradot_physics_cuda", "bradot_physics_server_cuda.cpp"), os.path.join(HERE, "bradot_physics_cuda", "register_types.cpp"),
             os.path.join(HERE, "engine_demo.cpp"), os.path.join(ROOT, "oracle", "ref_stubs.cpp")]

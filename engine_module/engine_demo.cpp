@@ -1,7 +1,10 @@
 // engine_demo -- proves the drop-in path end to end: brings up the engine core (the reference's own objects,
 // linked from oracle/_ref/libbradot_ref.a), registers "BradotPhysicsCUDA" with PhysicsServer3DManager, asks the
 // manager for that server BY NAME, builds a scene file through the public PhysicsServer3D RID API and steps it.
-// Body transforms after the last step go to stdout as JSON for comparison with a direct C-ABI run.
+// Every body gets a state-sync callback (what RigidBody3D registers, scene/3d/physics/rigid_body_3d.cpp:822); a script of
+// body_set_state / free events (same records as oracle/ref_harness.cpp --events) can be applied through the RID API.
+// Body transforms after the last step -- as body_get_state returns them and as the callbacks last reported them -- go to
+// stdout as JSON for comparison with a direct C-ABI run and with the reference's run of the same script.
 // Host code only (no CUDA here): it reaches the GPU solely through libbradot_physics_cuda.so.
 #include "core/config/engine.h"
 #include "core/config/project_settings.h"
@@ -31,11 +34,23 @@ public:
 };
 
 #pragma pack(push, 1)
-struct ScnHeader { char magic[4]; uint32_t version, n_spaces, n_shapes, n_bodies, n_joints, n_verts; float dt; uint32_t iterations, reserved[7]; };
+struct ScnHeader { char magic[4]; uint32_t version, n_spaces, n_shapes, n_bodies, n_joints, n_verts; float dt; uint32_t iterations, iter_step, reserved[6]; };
 struct ScnShape { uint32_t type; float p[4]; uint32_t vert_ofs, vert_cnt, pad; };
 struct ScnBody { uint32_t space, mode, shape, flags; float xf[12], shape_xf[12], linvel[3], angvel[3], mass, friction, bounce, gravity_scale, lin_damp, ang_damp; uint32_t layer, mask; };
-struct ScnJoint { uint32_t type, body_a, body_b, flags; float fa[12], fb[12]; };
+struct ScnJoint { uint32_t type, body_a, body_b, flags; float fa[12], fb[12], params[8]; uint32_t priority, pad[3]; };
+struct Event { int32_t step, body, kind; float v[12]; };
 #pragma pack(pop)
+
+// what the state-sync callbacks reported: last transform per body, number of calls
+static std::vector<Transform3D> g_synced;
+static std::vector<int> g_sync_calls;
+static void on_state_sync(Object *p_state, int p_index) {
+	PhysicsDirectBodyState3D *st = Object::cast_to<PhysicsDirectBodyState3D>(p_state);
+	if (st && p_index >= 0 && p_index < (int)g_synced.size()) {
+		g_synced[p_index] = st->get_transform();
+		g_sync_calls[p_index]++;
+	}
+}
 
 static Transform3D xf_from(const float *f) {
 	return Transform3D(Basis(f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7], f[8]), Vector3(f[9], f[10], f[11]));
@@ -43,13 +58,29 @@ static Transform3D xf_from(const float *f) {
 
 int main(int argc, char **argv) {
 	if (argc < 3) {
-		fprintf(stderr, "usage: engine_demo scene.bscn steps\n");
+		fprintf(stderr, "usage: engine_demo scene.bscn steps [--events events.bin]\n");
 		return 2;
 	}
 	int steps = atoi(argv[2]);
+	std::vector<Event> events;
+	for (int i = 3; i + 1 < argc; i++) {
+		if (strcmp(argv[i], "--events") == 0) {
+			FILE *ef = fopen(argv[i + 1], "rb");
+			uint32_t ne = 0;
+			if (!ef || fread(&ne, 4, 1, ef) != 1) {
+				fprintf(stderr, "cannot read events\n");
+				return 2;
+			}
+			events.resize(ne);
+			if (ne && fread(events.data(), sizeof(Event), ne, ef) != ne) {
+				return 2;
+			}
+			fclose(ef);
+		}
+	}
 	FILE *sf = fopen(argv[1], "rb");
 	ScnHeader hd;
-	if (!sf || fread(&hd, sizeof(hd), 1, sf) != 1 || memcmp(hd.magic, "BSCN", 4) != 0) {
+	if (!sf || fread(&hd, sizeof(hd), 1, sf) != 1 || memcmp(hd.magic, "BSCN", 4) != 0 || hd.version != 2) {
 		fprintf(stderr, "bad scene file\n");
 		return 2;
 	}
@@ -88,7 +119,7 @@ int main(int argc, char **argv) {
 	for (uint32_t i = 0; i < hd.n_spaces; i++) {
 		RID sp = ps->space_create();
 		ps->space_set_active(sp, true);
-		ps->space_set_param(sp, PhysicsServer3D::SPACE_PARAM_SOLVER_ITERATIONS, hd.iterations);
+		ps->space_set_param(sp, PhysicsServer3D::SPACE_PARAM_SOLVER_ITERATIONS, hd.iterations + i * hd.iter_step);
 		space_r.push_back(sp);
 	}
 	for (const ScnShape &s : shapes) {
@@ -147,52 +178,112 @@ int main(int argc, char **argv) {
 		if (b.flags & 2) {
 			ps->body_set_enable_continuous_collision_detection(body, true);
 		}
+		if (b.flags & 16) {
+			ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_LINEAR_DAMP_MODE, PhysicsServer3D::BODY_DAMP_MODE_REPLACE);
+		}
+		if (b.flags & 32) {
+			ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_ANGULAR_DAMP_MODE, PhysicsServer3D::BODY_DAMP_MODE_REPLACE);
+		}
+		for (int ax = 0; ax < 6; ax++) {
+			if ((b.flags >> 8) & (1u << ax)) {
+				ps->body_set_axis_lock(body, (PhysicsServer3D::BodyAxis)(1 << ax), true);
+			}
+		}
 		ps->body_set_space(body, space_r[b.space]);
+		ps->body_set_state_sync_callback(body, callable_mp_static(&on_state_sync).bind((int)body_r.size()));
 		body_r.push_back(body);
 	}
+	g_synced.resize(body_r.size());
+	g_sync_calls.assign(body_r.size(), 0);
+	std::vector<char> freed(body_r.size(), 0);
 	// scene flag bit3: pushed before every step, the same push as oracle/ref_harness.cpp push_bodies()
 	auto push = [&]() {
 		for (size_t i = 0; i < body_r.size(); i++) {
-			if (bodies[i].flags & 8) {
+			if ((bodies[i].flags & 8) && !freed[i]) {
 				ps->body_apply_central_force(body_r[i], Vector3(0.5f * (float)((int)(i % 3) - 1), 2.0f, 0.3f));
 				ps->body_apply_torque(body_r[i], Vector3(0.1f, 0.0f, 0.05f * (float)(i % 2)));
 			}
 		}
 	};
-	push();
-	ps->step(hd.dt); // uploads the bodies; joints need uploaded bodies, so they are made after the first tick here
+	std::vector<RID> joint_r;
 	for (const ScnJoint &j : joints) {
 		RID jr = ps->joint_create();
 		if (j.type == 0) {
 			ps->joint_make_pin(jr, body_r[j.body_a], Vector3(j.fa[9], j.fa[10], j.fa[11]), body_r[j.body_b], Vector3(j.fb[9], j.fb[10], j.fb[11]));
+			if (j.flags & 8) {
+				for (int k = 0; k < 3; k++) {
+					ps->pin_joint_set_param(jr, (PhysicsServer3D::PinJointParam)k, j.params[k]);
+				}
+			}
 		} else {
 			ps->joint_make_hinge(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
+			if (j.flags & 8) {
+				for (int k = 0; k < (int)PhysicsServer3D::HINGE_JOINT_MAX; k++) {
+					ps->hinge_joint_set_param(jr, (PhysicsServer3D::HingeJointParam)k, j.params[k]);
+				}
+			}
+			ps->hinge_joint_set_flag(jr, PhysicsServer3D::HINGE_JOINT_FLAG_USE_LIMIT, (j.flags & 2) != 0);
+			ps->hinge_joint_set_flag(jr, PhysicsServer3D::HINGE_JOINT_FLAG_ENABLE_MOTOR, (j.flags & 4) != 0);
 		}
 		if (j.flags & 1) {
 			ps->joint_disable_collisions_between_bodies(jr, true);
 		}
+		if (j.priority) {
+			ps->joint_set_solver_priority(jr, (int)j.priority);
+		}
+		joint_r.push_back(jr);
 	}
-	for (int s = 1; s < steps; s++) {
+	// the engine's tick (main/main.cpp:4368-4397): sync -> flush_queries (callbacks) -> [user code] -> end_sync -> step
+	for (int s = 1; s <= steps; s++) {
 		ps->sync();
 		ps->flush_queries();
+		for (const Event &e : events) { // "user code": the script, through the RID API
+			if (e.step != s || e.body < 0 || e.body >= (int)body_r.size() || freed[e.body]) {
+				continue;
+			}
+			RID body = body_r[e.body];
+			switch (e.kind) {
+				case 0: ps->body_set_state(body, PhysicsServer3D::BODY_STATE_TRANSFORM, xf_from(e.v)); break;
+				case 1: ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(e.v[0], e.v[1], e.v[2])); break;
+				case 2: ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(e.v[0], e.v[1], e.v[2])); break;
+				case 3:
+					ps->free(body);
+					freed[e.body] = 1;
+					break;
+				case 4: ps->body_set_state(body, PhysicsServer3D::BODY_STATE_SLEEPING, e.v[0] != 0.f); break;
+				case 5: ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, e.v[0] != 0.f); break;
+			}
+		}
 		ps->end_sync();
 		push();
 		ps->step(hd.dt);
 	}
 	ps->sync();
+	ps->flush_queries(); // the callbacks of the last step
+	ps->end_sync();
+	ps->sync();
 	printf("{\"server\": \"BradotPhysicsCUDA\", \"steps\": %d, \"active_objects\": %d, \"collision_pairs\": %d, \"island_count\": %d, \"origins\": [",
 			steps, ps->get_process_info(PhysicsServer3D::INFO_ACTIVE_OBJECTS), ps->get_process_info(PhysicsServer3D::INFO_COLLISION_PAIRS),
 			ps->get_process_info(PhysicsServer3D::INFO_ISLAND_COUNT));
 	for (size_t i = 0; i < body_r.size(); i++) {
-		Transform3D t = ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM);
+		Transform3D t = freed[i] ? Transform3D() : Transform3D(ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM));
 		printf("%s[%.9g, %.9g, %.9g]", i ? ", " : "", t.origin.x, t.origin.y, t.origin.z);
+	}
+	printf("], \"synced\": [");
+	for (size_t i = 0; i < body_r.size(); i++) { // last transform each body's state-sync callback reported, number of calls
+		const Transform3D &t = g_synced[i];
+		printf("%s[%d, %.9g, %.9g, %.9g]", i ? ", " : "", freed[i] ? -1 : g_sync_calls[i], t.origin.x, t.origin.y, t.origin.z);
+	}
+	printf("], \"sleeping\": [");
+	for (size_t i = 0; i < body_r.size(); i++) {
+		printf("%s%d", i ? ", " : "", freed[i] ? -1 : (int)(bool)ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_SLEEPING));
 	}
 	printf("], \"rays\": [");
 	// PhysicsDirectSpaceState3D::intersect_ray through the RID API: straight down onto the first bodies
 	PhysicsDirectSpaceState3D *ds = ps->space_get_direct_state(space_r[0]);
 	int n_rays = body_r.size() < 16 ? (int)body_r.size() : 16;
 	for (int i = 0; ds && i < n_rays; i++) {
-		Transform3D t = ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM);
+		Transform3D t = freed[i] ? Transform3D() : Transform3D(ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM));
 		PhysicsDirectSpaceState3D::RayParameters rp;
 		rp.from = Vector3(t.origin.x, 30.0, t.origin.z);
 		rp.to = Vector3(t.origin.x, -1.0, t.origin.z);

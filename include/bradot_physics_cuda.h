@@ -80,7 +80,9 @@ enum {
      * VELOCITY = constant linear + angular velocity (6 floats) added to the derived ones: what BODY_STATE_LINEAR_VELOCITY /
      * ANGULAR_VELOCITY mean for a kinematic body (constant_linear_velocity, bradot_body_3d.cpp:383-393). */
     BPC_FIELD_KINEMATIC_TARGET = 8,
-    BPC_FIELD_KINEMATIC_VELOCITY = 9
+    BPC_FIELD_KINEMATIC_VELOCITY = 9,
+    BPC_FIELD_CONSTANT_FORCE = 10,  /* 6 floats: constant force, constant torque (body_set_constant_force / _torque, P3D/bradot_body_3d.h:257-281); a non-zero row wakes its body */
+    BPC_FIELD_MASS_WORLD = 11       /* read only, 13 floats: world inverse inertia tensor rows (9), world-oriented centre of mass (3), inverse mass */
 };
 
 typedef struct bpc_stats {
@@ -159,6 +161,11 @@ int bpc_bodies_read_slots(bpc_context *ctx, int field, const int32_t *slots, int
 int bpc_bodies_write_slots(bpc_context *ctx, int field, const int32_t *slots, int n, const float *host);
 /* Transform (12), linear velocity (3), angular velocity (3), active (1) of every body in one call: 19 floats per body. */
 int bpc_bodies_read_state(bpc_context *ctx, int first, int n, float *host);
+
+/* body_add_collision_exception / body_remove_collision_exception (P3D/bradot_physics_server_3d.cpp:690-720): the pair
+ * (a, b) is skipped by the narrowphase as long as the exception stands (joints that disable collisions between their bodies
+ * add theirs on their own). */
+int bpc_bodies_set_exception(bpc_context *ctx, int body_a, int body_b, int excepted);
 
 /* Size every per-body and per-pair buffer for `bodies` bodies and `pairs` broadphase pairs up front, so that bpc_step does
  * not allocate while the counts stay below them (a pair burst beyond `pairs` still grows the buffers, once). */

@@ -22,6 +22,16 @@ def have_oracle():
 EVENT_DT = np.dtype([("step", "<i4"), ("body", "<i4"), ("kind", "<i4"), ("v", "<f4", 12)])
 
 
+def write_events(path, events):
+    """(step, body, kind, values) records in the file format oracle_step and engine_demo read (--events)."""
+    ev = np.zeros(len(events), EVENT_DT)
+    for i, (step, body, kind, v) in enumerate(events):
+        ev[i] = (step, body, kind, v)
+    with open(path, "wb") as f:
+        f.write(np.uint32(len(ev)).tobytes())
+        f.write(ev.tobytes())
+
+
 def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays=None, state=None, events=None, warmup=0, slim=False, dump_steps=None):
     """Step `sc` with the reference; returns (timing dict, dump dict).  `rays` (n, 6) float32 from/to: every dumped step
     also holds ("rays", step) = the reference's intersect_ray answers in space 0.  `state` (n_bodies, 18): transforms and
@@ -50,13 +60,8 @@ def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays
             f.write(st.tobytes())
         cmd += ["--state", extra[-1]]
     if events is not None:
-        ev = np.zeros(len(events), EVENT_DT)
-        for i, (step, body, kind, v) in enumerate(events):
-            ev[i] = (step, body, kind, v)
         extra.append(os.path.join(d, "events.bin"))
-        with open(extra[-1], "wb") as f:
-            f.write(np.uint32(len(ev)).tobytes())
-            f.write(ev.tobytes())
+        write_events(extra[-1], events)
         cmd += ["--events", extra[-1]]
     if warmup:
         cmd += ["--warmup", str(warmup)]

@@ -79,3 +79,51 @@ def test_engine_module_forces_and_ccd_match_direct_c_abi(tmp_path, name):
     if name == "bullets":
         ccd = (sc.bodies["flags"] & 2) != 0
         assert np.all(direct[ccd, 2] < 3.0)        # stopped by the wall / the plates
+
+
+def test_engine_module_callbacks_set_state_and_free_match_c_abi_and_reference(tmp_path):
+    """A scene driven like a game drives it -- every body has a state-sync callback (what RigidBody3D registers), a script of
+    body_set_state / free calls runs between the ticks -- through the RID API of the module, against (1) the same script on
+    the C ABI directly: bit-equal; (2) the reference running the same script (oracle_step --events): same sleep state for
+    every body, positions to 2 mm; and the transforms the callbacks reported are the ones body_get_state returns."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    if not parity.have_oracle():
+        pytest.skip("oracle/_ref/oracle_step not built")
+    sc = scenes.scripted_events()
+    events = scenes.scripted_events_script()
+    steps = 160
+    path, evp = str(tmp_path / "scene.bscn"), str(tmp_path / "events.bin")
+    sc.write(path)
+    parity.write_events(evp, events)
+    r = subprocess.run([DEMO, path, str(steps), "--events", evp], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    engine = np.array(out["origins"], np.float32)
+    synced = np.array(out["synced"], np.float64)
+    sleeping = np.array(out["sleeping"])
+    freed = {body for (_, body, kind, _) in events if kind == 3}
+    alive = np.array([i not in freed for i in range(len(sc.bodies))])
+    dyn = sc.bodies["mode"] >= scenes.MODE_RIGID
+    # (1) the C ABI directly
+    from test_gpu_features import _apply_events
+    ps = parity.new_server(sc)
+    gone = set()
+    for s in range(1, steps + 1):
+        _apply_events(ps, events, s, gone)
+        ps.step(sc.dt)
+    st = ps.bodies_read_state()
+    ps.finish()
+    assert np.array_equal(engine[alive], st[alive, 9:12]), float(np.abs(engine[alive] - st[alive, 9:12]).max())
+    assert np.array_equal(sleeping[alive & dyn] == 0, st[alive & dyn, 18] != 0)
+    # (2) the reference
+    _, dump = parity.run_oracle(sc, steps, events=events, dump_steps=[steps])
+    ref = dump[("bodies", steps)]
+    assert np.max(np.abs(engine[alive] - ref[alive, 9:12])) < 2e-3
+    assert np.array_equal(sleeping[alive & dyn] == 0, ref[alive & dyn, 18] != 0)
+    # the callbacks: every moving body was told, freed ones are marked, and the last reported transform is the current one
+    calls = synced[:, 0]
+    assert np.all(calls[~alive] == -1) and np.all(calls[alive & dyn] > 0) and np.all(calls[alive & ~dyn] == 0)
+    assert np.array_equal(synced[alive & dyn, 1:4].astype(np.float32), engine[alive & dyn])
+    # a body asleep for most of the run was told far fewer times than there were ticks
+    assert calls[4] < steps // 2
