@@ -150,7 +150,7 @@ extern "C" int bpc_step(bpc_context *ctx, float dt) {
     if (bpc_launch_narrowphase(ctx)) return -1;
     if (bpc_launch_joint_setup(ctx, dt)) return -1;
     uint32_t np = ctx->n_pairs[ctx->cur];
-    if (np) {
+    if (np) { // (folding this count into k_con_collect was measured: two atomic streams on one line, 0.39 ms instead of 0.14 + 0.13)
         k_count_collided<<<nblk(np, 128), 128, 0, st>>>(np, ctx->pair_hdr[ctx->cur].p, ctx->counters.p);
         ctx->launches += 1;
     }
