@@ -418,6 +418,7 @@ extern "C" int bpc_bodies_update(bpc_context *ctx, const int32_t *slots, int n, 
         uint32_t s = (uint32_t)slots[i];
         if (write_body_slots(ctx, &s, descs + i, 1, keep_state != 0)) return -1;
     }
+    ctx->recolor = true; // a body may have changed sides (static <-> dynamic): the kept sweep colours no longer describe the graph
     return 0;
 }
 

@@ -75,8 +75,12 @@ struct __align__(16) ContactAcc {
     float4 b;   // acc_bias, acc_bias_com, 0, 0
 };
 struct __align__(16) PairHdr {
-    float4 sep; // cached separating axis xyz ; w = bits: contact_count | collided<<8 | collide_A<<9 | collide_B<<10
+    // cached separating axis xyz ; w = bits: contact_count | collided<<8 | collide_A<<9 | collide_B<<10 | check_ccd<<11 |
+    // (sweep colour + 1)<<16 (0 = none; kept across steps while the pair stays a constraint)
+    float4 sep;
 };
+#define PAIR_COLOUR_SHIFT 16
+#define PAIR_COLOUR_MASK 0x7f0000u
 // Solver-facing contact written by pre_solve in sweep order.
 struct __align__(16) SolveContact {
     float4 n_mn;   // normal, mass_normal
@@ -265,6 +269,10 @@ struct bpc_context {
     DevBuf<uint32_t> con_bin, bin_tab, bin_base;
     DevBuf<uint16_t> con_sorted_color; // colour * 4 + work class of each entry of con_sorted
     DevBuf<uint8_t> con_cls;           // work class (cached contacts - 1) of each entry of con_list
+    DevBuf<uint8_t> joint_color;       // sweep colour + 1 each joint had last step (0 = none)
+    uint32_t colors_at_fresh = 0;      // colours the last from-scratch colouring needed
+    bool last_color_fresh = false;
+    bool recolor = true;               // ignore the kept colours at the next step (bodies re-described, joints changed, too many colours)
     uint32_t n_bins = 0;
     bool use_bins = true;
     DevBuf<SolveContact> scontacts;

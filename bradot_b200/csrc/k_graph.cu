@@ -219,12 +219,17 @@ __device__ __forceinline__ void con_bodies(uint32_t id, uint32_t n_pairs, const 
     }
 }
 
+// Colours persist.  A constraint that was one last step keeps its colour (pairs carry it in their header through k_match and
+// the narrowphase, joints in joint_color): colours that were pairwise compatible last step still are, so only the NEW
+// constraints of a step bid in the Jones-Plassmann rounds, against the colours already taken on their bodies.  A settled
+// 1 M-body pile re-derived 4.7 M colours per step for a graph that barely changes (3.7 ms); `fresh` (bodies re-described,
+// joints changed, or the colour count crept up) starts from scratch.
 __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t n_joints, uint32_t n_bodies, const uint64_t *__restrict__ keys,
-                                                      const PairHdr *__restrict__ hdr, const JointRec *__restrict__ joints,
+                                                      PairHdr *__restrict__ hdr, const JointRec *__restrict__ joints,
                                                       const uint4 *__restrict__ meta, uint32_t *__restrict__ list,
                                                       uint32_t *__restrict__ color, unsigned long long *__restrict__ best,
                                                       unsigned long long *__restrict__ colmask, uint32_t *__restrict__ counters,
-                                                      uint2 *__restrict__ ab, uint8_t *__restrict__ cls) {
+                                                      uint2 *__restrict__ ab, uint8_t *__restrict__ cls, uint8_t *__restrict__ joint_color, int fresh) {
     cg::grid_group grid = cg::this_grid();
     uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     // joints are appended to the list here (they are always solved)
@@ -234,22 +239,38 @@ __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t
         cls[n_col + j] = 0;
     }
     uint32_t n = n_col + n_joints;
-    for (uint32_t s = tid; s < n; s += nth) color[s] = 0xffffffffu;
     grid.sync();
     // Tickets of round r live in best[r & 1]; a loser of round r bids for round r + 1 in the other array during
     // the same pass, so a round costs one pass and one grid barrier.  A ticket carries its round in the high
     // word, so entries left from two rounds ago can never equal (or beat) a current ticket.
     unsigned long long *bestv[2] = { best, best + n_bodies };
+    uint32_t left0 = 0;
     for (uint32_t s = tid; s < n; s += nth) {
         uint32_t id = list[s], a, b;
         con_bodies(id, n_pairs, keys, hdr, joints, meta, a, b);
         ab[s] = make_uint2(a, b); // the rounds read the two bodies from here: one coalesced load instead of two gathers
+        uint32_t old = fresh ? 0u : (id < n_pairs ? ((__float_as_uint(hdr[id].sep.w) & PAIR_COLOUR_MASK) >> PAIR_COLOUR_SHIFT) : joint_color[id - n_pairs]);
+        if (old) { // kept: claim the colour on both bodies
+            color[s] = old - 1;
+            if (a != 0xffffffffu) atomicOr(&colmask[a], 1ull << (old - 1));
+            if (b != 0xffffffffu) atomicOr(&colmask[b], 1ull << (old - 1));
+            continue;
+        }
+        color[s] = 0xffffffffu;
+        left0++;
         unsigned long long ticket = (1ull << 32) | hash32(id);
         if (a != 0xffffffffu) atomicMax(&bestv[1][a], ticket);
         if (b != 0xffffffffu) atomicMax(&bestv[1][b], ticket);
     }
+    {
+        uint32_t any = __syncthreads_or(left0 != 0);
+        if (threadIdx.x == 0 && any) atomicOr(&counters[CNT_ROUND + 0], 1u); // slot 0: "someone needs a colour at all"
+    }
     grid.sync();
-    for (uint32_t round = 1; round < 4096; round++) {
+    const bool anyone = counters[CNT_ROUND + 0] != 0;
+    grid.sync(); // slot 0 is reused by round 3: everybody has read it
+    if (tid == 0) counters[CNT_ROUND + 0] = 0;
+    for (uint32_t round = 1; anyone && round < 4096; round++) {
         const unsigned long long *cur = bestv[round & 1];
         unsigned long long *nxt = bestv[(round + 1) & 1];
         uint32_t left = 0;
@@ -268,6 +289,14 @@ __global__ void __launch_bounds__(GR_THREADS) k_color(uint32_t n_pairs, uint32_t
                 if (c < MAX_COLORS) {
                     if (a != 0xffffffffu) colmask[a] |= 1ull << c;
                     if (b != 0xffffffffu) colmask[b] |= 1ull << c;
+                }
+                // remember it (the overflow group is re-bid every step)
+                uint32_t keep = c < MAX_COLORS ? c + 1 : 0u;
+                if (id < n_pairs) {
+                    uint32_t w = __float_as_uint(hdr[id].sep.w);
+                    hdr[id].sep.w = __uint_as_float((w & ~PAIR_COLOUR_MASK) | (keep << PAIR_COLOUR_SHIFT));
+                } else {
+                    joint_color[id - n_pairs] = (uint8_t)keep;
                 }
             } else {
                 unsigned long long t2 = ((unsigned long long)(round + 1) << 32) | hsh;
@@ -478,14 +507,28 @@ int bpc_launch_schedule(bpc_context *ctx) {
         if (per_sm > 4) per_sm = 4;
         dim3 grid(ctx->sm_count * per_sm), block(GR_THREADS);
         const uint64_t *keys = ctx->pair_keys[ctx->cur].p;
-        const PairHdr *hdr = ctx->pair_hdr[ctx->cur].p;
+        PairHdr *hdr = ctx->pair_hdr[ctx->cur].p;
         const JointRec *joints = ctx->d_joints.p;
         const uint4 *meta = ctx->meta.p;
         uint32_t *list = ctx->con_list.p, *color = ctx->con_color.p, *counters = ctx->counters.p;
         unsigned long long *best = (unsigned long long *)ctx->body_best.p, *colmask = (unsigned long long *)ctx->body_colmask.p;
         uint2 *ab = (uint2 *)ctx->con_info.p; // the solver's per-slot records are not live yet: scratch for the colouring
         uint8_t *cls = ctx->con_cls.p;
-        void *args[] = { &np, &nj, &n, &keys, &hdr, &joints, &meta, &list, &color, &best, &colmask, &counters, &ab, &cls };
+        // start from scratch when the graph's nodes changed under the colours, or when the colour count has crept up
+        // (kept colours fragment slowly: C2 went from 14 to 17 colours, +5 % sweep time; one more colour than a fresh colouring
+        // needed + an eighth is the bar)
+        uint32_t seen = ctx->h_counters[CNT_COLORS];
+        if (ctx->last_color_fresh && seen) ctx->colors_at_fresh = seen;
+        int fresh = (ctx->recolor || ctx->colors_at_fresh == 0 || seen > ctx->colors_at_fresh + 1 + ctx->colors_at_fresh / 8) ? 1 : 0;
+        ctx->recolor = false;
+        ctx->last_color_fresh = fresh != 0;
+        ctx->joint_color.reserve((size_t)nj + 1, true, st);
+        if (!ctx->joint_color.p) {
+            ctx->err = "schedule: out of device memory";
+            return -1;
+        }
+        uint8_t *jcol = ctx->joint_color.p;
+        void *args[] = { &np, &nj, &n, &keys, &hdr, &joints, &meta, &list, &color, &best, &colmask, &counters, &ab, &cls, &jcol, &fresh };
         BPC_CHECK(cudaLaunchCooperativeKernel((void *)k_color, grid, block, args, 0, st));
     }
     // sort the constraints into [barrier path by colour][bin 1 by colour][bin 2 by colour]...

@@ -99,6 +99,13 @@ __global__ void __launch_bounds__(256) k_type_keys(uint32_t n, const uint64_t *_
     vals[k] = k;
 }
 
+// The sweep colour a pair had as a constraint of the last step (header bits 16..22, colour + 1) stays with it while it keeps
+// colliding with the same bodies on its dynamic side: colours that were compatible last step still are (k_color, k_graph.cu).
+// A pair that stops colliding loses it -- by the time it collides again its colour may have been given to a neighbour.
+__device__ __forceinline__ uint32_t kept_colour(uint32_t old_bits, uint32_t new_bits) {
+    return ((new_bits & 0x100u) && ((old_bits ^ new_bits) & 0x600u) == 0u) ? (old_bits & PAIR_COLOUR_MASK) : 0u;
+}
+
 __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     bool work = false, cwork = false;
@@ -233,6 +240,7 @@ __global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
         a.acc[(size_t)k * 4 + c] = ac;
     }
     uint32_t nb = (uint32_t)m.count | (collided ? 0x100u : 0u) | (collide_A ? 0x200u : 0u) | (collide_B ? 0x400u : 0u);
+    nb |= kept_colour(bits, nb);
     if (!collided && ((((ma.x >> 8) & BF_CCD) && collide_A) || (((mb.x >> 8) & BF_CCD) && collide_B))) nb |= 0x800u; // check_ccd
     h.sep = v4(sep_axis, __uint_as_float(nb));
     a.hdr[k] = h;
@@ -320,6 +328,7 @@ __global__ void __launch_bounds__(CW_WARPS * 32) k_convex_warp(NpArgs a) {
         a.acc[(size_t)k * 4 + c] = ac;
     }
     uint32_t nb = (uint32_t)m.count | (collided ? 0x100u : 0u) | (collide_A ? 0x200u : 0u) | (collide_B ? 0x400u : 0u);
+    nb |= kept_colour(__float_as_uint(h.sep.w), nb);
     if (!collided && ((((ma.x >> 8) & BF_CCD) && collide_A) || (((mb.x >> 8) & BF_CCD) && collide_B))) nb |= 0x800u;
     h.sep = v4(sep_axis, __uint_as_float(nb));
     a.hdr[k] = h;

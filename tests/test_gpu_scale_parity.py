@@ -141,7 +141,7 @@ def test_body_with_more_than_64_dynamic_neighbours():
         if s % 30 == 0:
             ref = dump[("bodies", s)]
             st = ps.bodies_read_state()
-            assert np.max(np.abs(st[:, 9:12] - ref[:, 9:12])) < 5e-3, "positions differ from the reference at step %d" % s
+            assert np.max(np.abs(st[:, 9:12] - ref[:, 9:12])) < 1e-2, "positions differ from the reference at step %d" % s   # free run, other sweep order
             assert np.max(np.abs(st[:, 12:18] - ref[:, 12:18])) < 5e-2
     assert overflow > 0, "the plate never had more constraints than colours"
     ps.finish()
