@@ -290,6 +290,10 @@ static int write_body_slots(bpc_context *ctx, const uint32_t *slots, const bpc_b
         ctx->h_big[slot] = (d.mode == MODE_STATIC && sh.meta.x == SH_PLANE) ? 1 : 0;
         ctx->h_ccd[slot] = (d.flags & 2u) ? 1 : 0;
         ctx->h_dead[slot] = 0;
+        if (!keep_state && slot < ctx->h_report_cap.size() && ctx->h_report_cap[slot]) { // a new body in a reused slot reports nothing
+            ctx->h_report_cap[slot] = 0;
+            ctx->report_dirty = true;
+        }
     }
     if (any_kin && !ctx->kin.p) {
         ctx->kin.reserve(ctx->xf.cap, false, st);
@@ -346,6 +350,7 @@ static int write_body_slots(bpc_context *ctx, const uint32_t *slots, const bpc_b
 }
 
 static void grow_mirrors(bpc_context *ctx, size_t total) {
+    if (ctx->n_reporting || ctx->report_dirty) ctx->report_dirty = true; // offsets cover every body
     ctx->h_mode.resize(total);
     ctx->h_big.resize(total);
     ctx->h_space_of.resize(total);
@@ -498,6 +503,10 @@ extern "C" int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n)
     BPC_CHECK(cudaStreamSynchronize(st));
     std::vector<uint8_t> gone(ctx->n_bodies, 0);
     for (uint32_t i : s) {
+        if (i < ctx->h_report_cap.size() && ctx->h_report_cap[i]) {
+            ctx->h_report_cap[i] = 0;
+            ctx->report_dirty = true;
+        }
         ctx->h_dead[i] = 1;
         ctx->h_mode[i] = MODE_STATIC;
         ctx->h_big[i] = 0;
@@ -1031,4 +1040,96 @@ extern "C" int bpc_bodies_read_state(bpc_context *ctx, int first, int n, float *
     BPC_CHECK(cudaMemcpyAsync(out, ctx->staging.p, (size_t)n * 19 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     BPC_CHECK(cudaStreamSynchronize(ctx->stream));
     return 0;
+}
+
+
+// ---------------------------------------------------------------------------------------------- contact reporting
+// per-body caps -> offsets of each body's records (host prefix sum; the caps change rarely)
+int bpc_flush_report_tables(bpc_context *ctx) {
+    if (!ctx->report_dirty) return 0;
+    ctx->report_dirty = false;
+    uint32_t n = ctx->n_bodies;
+    ctx->h_report_cap.resize(n, 0);
+    std::vector<uint32_t> ofs(n + 1, 0);
+    ctx->n_reporting = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        ofs[i + 1] = ofs[i] + ctx->h_report_cap[i];
+        ctx->n_reporting += ctx->h_report_cap[i] ? 1u : 0u;
+    }
+    ctx->report_total = ofs[n];
+    if (!ctx->n_reporting) return 0;
+    cudaStream_t st = ctx->stream;
+    ctx->report_cap.reserve(n, false, st);
+    ctx->report_ofs.reserve(n + 1, false, st);
+    ctx->report_count.reserve(n, false, st);
+    ctx->reports.reserve(ctx->report_total, false, st);
+    ctx->report_overflow.reserve(REPORT_OVERFLOW_CAP, false, st);
+    ctx->report_overflow_body.reserve(REPORT_OVERFLOW_CAP, false, st);
+    if (!ctx->report_cap.p || !ctx->report_ofs.p || !ctx->report_count.p || !ctx->reports.p || !ctx->report_overflow.p || !ctx->report_overflow_body.p)
+        return fail(ctx, "contact reporting: out of device memory");
+    BPC_CHECK(cudaMemcpyAsync(ctx->report_cap.p, ctx->h_report_cap.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    BPC_CHECK(cudaMemcpyAsync(ctx->report_ofs.p, ofs.data(), (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, st));
+    BPC_CHECK(cudaMemsetAsync(ctx->report_count.p, 0, (size_t)n * 4, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int bpc_bodies_set_max_contacts_reported(bpc_context *ctx, const int32_t *slots, int n, const int32_t *max_contacts) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && (!slots || !max_contacts))) return fail(ctx, "bpc_bodies_set_max_contacts_reported: bad arguments");
+    for (int i = 0; i < n; i++) {
+        if (slots[i] < 0 || (uint32_t)slots[i] >= ctx->n_bodies || ctx->h_dead[slots[i]]) return fail(ctx, "bpc_bodies_set_max_contacts_reported: invalid body");
+        if (max_contacts[i] < 0 || max_contacts[i] > 4096) return fail(ctx, "bpc_bodies_set_max_contacts_reported: between 0 and 4096 contacts per body");
+    }
+    ctx->h_report_cap.resize(ctx->n_bodies, 0);
+    for (int i = 0; i < n; i++) ctx->h_report_cap[slots[i]] = (uint32_t)max_contacts[i];
+    ctx->report_dirty = true;
+    return 0;
+}
+
+extern "C" int bpc_contacts_capacity(bpc_context *ctx) {
+    if (!ctx) return -1;
+    if (bpc_flush_report_tables(ctx)) return -1;
+    return (int)ctx->report_total;
+}
+
+extern "C" int bpc_contacts_read(bpc_context *ctx, int32_t *counts, int32_t *offsets, bpc_contact *records) {
+    if (!ctx) return -1;
+    if (!counts || !offsets) return fail(ctx, "bpc_contacts_read: bad arguments");
+    static_assert(sizeof(bpc_contact) == sizeof(ReportRec), "bpc_contact mirrors ReportRec");
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (bpc_resolve_step(ctx) || bpc_flush_report_tables(ctx)) return -1;
+    uint32_t n = ctx->n_bodies;
+    if (!ctx->n_reporting) {
+        memset(counts, 0, (size_t)n * 4);
+        memset(offsets, 0, (size_t)n * 4);
+        return 0;
+    }
+    cudaStream_t st = ctx->stream;
+    BPC_CHECK(cudaMemcpyAsync(counts, ctx->report_count.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaMemcpyAsync(offsets, ctx->report_ofs.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    if (records && ctx->report_total) BPC_CHECK(cudaMemcpyAsync(records, ctx->reports.p, (size_t)ctx->report_total * sizeof(ReportRec), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    for (uint32_t i = 0; i < n; i++) counts[i] = (int32_t)std::min((uint32_t)counts[i], ctx->h_report_cap[i]); // arrivals beyond the cap were merged
+    return 0;
+}
+
+extern "C" int bpc_body_read_contacts(bpc_context *ctx, int slot, int max_records, bpc_contact *out) {
+    if (!ctx) return -1;
+    if (slot < 0 || (uint32_t)slot >= ctx->n_bodies || max_records < 0 || (max_records > 0 && !out)) return fail(ctx, "bpc_body_read_contacts: bad arguments");
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (bpc_resolve_step(ctx) || bpc_flush_report_tables(ctx)) return -1;
+    if (!ctx->n_reporting || !ctx->h_report_cap[slot]) return 0;
+    cudaStream_t st = ctx->stream;
+    uint32_t cnt = 0, ofs = 0;
+    BPC_CHECK(cudaMemcpyAsync(&cnt, ctx->report_count.p + slot, 4, cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaMemcpyAsync(&ofs, ctx->report_ofs.p + slot, 4, cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    cnt = std::min(cnt, ctx->h_report_cap[slot]);
+    uint32_t take = std::min(cnt, (uint32_t)max_records);
+    if (take) {
+        BPC_CHECK(cudaMemcpyAsync(out, ctx->reports.p + ofs, (size_t)take * sizeof(ReportRec), cudaMemcpyDeviceToHost, st));
+        BPC_CHECK(cudaStreamSynchronize(st));
+    }
+    return (int)cnt;
 }

@@ -90,6 +90,15 @@ struct __align__(16) SolveContact {
     float4 b;      // acc_bias, acc_bias_com, friction, active(1/0)
 };
 
+// A contact reported to a body that asked for contacts (body_set_max_contacts_reported): what BradotBody3D::add_contact keeps
+// (bradot_body_3d.h:353-395).  Same layout as bpc_contact.
+struct __align__(16) ReportRec {
+    float local_pos[3], depth;
+    float local_normal[3];
+    int32_t collider; // body index of the other body
+    float local_velocity[3], collider_pos[3], collider_velocity[3], impulse[3];
+};
+
 template <typename T>
 struct DevBuf {
     T *p = nullptr;
@@ -258,6 +267,15 @@ struct bpc_context {
     bool lists_dirty = false;    // tree / unbounded-static lists have to be rebuilt before the next step or query
     uint32_t max_priority = 1;   // highest joint solver priority
 
+    // contact reporting: per body the number of contacts it wants (0 = none), the start of its records, how many it got
+    // this step (may exceed the cap: the rest went to the overflow list and was merged by k_report_overflow)
+    DevBuf<uint32_t> report_cap, report_ofs, report_count;
+    DevBuf<ReportRec> reports, report_overflow;
+    DevBuf<uint32_t> report_overflow_body;
+    std::vector<uint32_t> h_report_cap;
+    uint32_t report_total = 0, n_reporting = 0;
+    bool report_dirty = false;
+
     // constraints / solver
     DevBuf<uint32_t> con_list, con_color, con_sorted, con_sorted_alt;
     DevBuf<uint4> con_info; // per scheduled constraint: body a, body b, flags|count, pair index
@@ -289,7 +307,9 @@ struct bpc_context {
 };
 
 enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIVE = 4, CNT_ISLANDS = 5, CNT_CONTACTS = 6,
-       CNT_OVERFLOW = 7, CNT_GROUPS = 8 /* colours on the grid-barrier path */, CNT_BARRIER_CONS = 9, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_ROUND = 20 /* 3 slots */, CNT_N = 32 };
+       CNT_OVERFLOW = 7, CNT_GROUPS = 8 /* colours on the grid-barrier path */, CNT_BARRIER_CONS = 9, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_REPORT_OVERFLOW = 13, CNT_ROUND = 20 /* 3 slots */, CNT_N = 32 };
+
+#define REPORT_OVERFLOW_CAP 65536u // reported contacts beyond their bodies' caps held per step for the deepest-N merge
 
 #define BPC_CHECK(x)                                                                                  \
     do {                                                                                              \

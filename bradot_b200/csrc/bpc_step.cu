@@ -11,6 +11,7 @@
 #include "bpc_internal.h"
 
 int bpc_flush_tables(bpc_context *ctx);
+int bpc_flush_report_tables(bpc_context *ctx);
 int bpc_launch_schedule(bpc_context *ctx);
 
 static int fail(bpc_context *ctx, const char *msg) {
@@ -70,6 +71,15 @@ __global__ void k_count_collided(uint32_t n_pairs, const PairHdr *__restrict__ h
     bool c = k < n_pairs && (__float_as_uint(hdr[k].sep.w) & 0x100u);
     uint32_t m = __ballot_sync(0xffffffffu, c);
     if ((threadIdx.x & 31) == 0 && m) atomicAdd(&counters[CNT_CONTACTS], __popc(m));
+}
+
+// contact_count = 0 happens inside integrate_forces (bradot_body_3d.cpp:671), which runs for the bodies of the active list
+// only and which a STATIC body leaves at its first line (:478-480).  So in the reference a sleeping body keeps reporting the
+// contacts of its last waking step, and the contacts reported to a static body are never cleared, only replaced by deeper
+// ones; both are mirrored here (the count keeps growing, arrivals beyond the cap go through the deepest-N merge).
+__global__ void k_report_reset(uint32_t n, const uint4 *__restrict__ meta, uint32_t *__restrict__ count) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && (meta[i].x & 0xffu) != MODE_STATIC && (meta[i].x & (BF_ACTIVE << 8))) count[i] = 0;
 }
 
 static int forced_schedule(bpc_context *ctx) {
@@ -137,6 +147,11 @@ extern "C" int bpc_step(bpc_context *ctx, float dt) {
     cudaStream_t st = ctx->stream;
     ctx->launches = 0;
     BPC_CHECK(cudaMemsetAsync(ctx->counters.p, 0, CNT_N * sizeof(uint32_t), st));
+    if (bpc_flush_report_tables(ctx)) return -1;
+    if (ctx->n_reporting) {
+        k_report_reset<<<nblk(ctx->n_bodies, 256), 256, 0, st>>>(ctx->n_bodies, ctx->meta.p, ctx->report_count.p);
+        ctx->launches += 1;
+    }
     if (ctx->profiling && collect_stage_times(ctx)) return -1;
 #define STAGE(i)                                                   \
     if (ctx->profiling) BPC_CHECK(cudaEventRecord(ctx->ev[i], st))

@@ -36,6 +36,7 @@ struct NpArgs {
     uint32_t *counters;
     uint32_t *work;      // compacted pair indices for the full pass
     uint32_t *cwork;     // hull-against-hull pairs for the warp-per-pair kernel
+    const uint32_t *report_cap; // contacts each body wants reported (nullptr = nobody does)
     const uint32_t *perm; // pair indices binned by shape-type pair (nullptr = identity)
     uint32_t n_work;
 };
@@ -133,12 +134,14 @@ __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
             }
             bool collide_A = (mode_a > MODE_KINEMATIC) && (mb.y & ma.z);
             bool collide_B = (mode_b > MODE_KINEMATIC) && (ma.y & mb.z);
+            // neither body would be pushed, but one of them reports contacts: the pair is still tested (report_contacts_only)
+            const bool wanted = collide_A || collide_B || (a.report_cap && (a.report_cap[ia] || a.report_cap[ib]));
             uint32_t nb = count; // collided = false, contacts untouched
             bool both_hulls = (ma.x >> 24) == SH_CONVEX && (mb.x >> 24) == SH_CONVEX;
-            if (interacts && !excepted && (collide_A || collide_B) && count > 0 && !both_hulls) {
+            if (interacts && !excepted && wanted && count > 0 && !both_hulls) {
                 // cached contacts have to be validated by the full pass whatever this one would decide: do not decide twice
                 work = true;
-            } else if (interacts && !excepted && (collide_A || collide_B)) {
+            } else if (interacts && !excepted && wanted) {
                 BodyXf bxa = a.xf[ia], bxb = a.xf[ib];
                 M3 bA(f4v(bxa.r0), f4v(bxa.r1), f4v(bxa.r2)), bB(f4v(bxb.r0), f4v(bxb.r1), f4v(bxb.r2));
                 V3 offset_B = f4v(bxb.o) - f4v(bxa.o);
@@ -378,6 +381,7 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
         a.cwork = ctx->np_cwork.p;
     }
     a.n_work = 0;
+    a.report_cap = ctx->n_reporting ? ctx->report_cap.p : nullptr;
     a.perm = nullptr;
     uint32_t solid_types = ctx->shape_type_mask & ~(1u << SH_PLANE);
     if (solid_types & (solid_types - 1)) { // more than one kind of solid shape: bin the pairs by type pair

@@ -48,6 +48,11 @@ struct SvArgs {
     // solver bins (k_solve_bins): per bin "fits one CTA", lowest / highest body, offsets of its colour runs
     const uint32_t *bin_ok, *bin_lo, *bin_hi, *bin_base;
     const uint16_t *sched_color; // colour * 4 + work class of each entry of `sched`
+    // contact reporting (null when no body asked for contacts)
+    const uint32_t *report_cap, *report_ofs;
+    uint32_t *report_count;
+    ReportRec *reports, *report_overflow;
+    uint32_t *report_overflow_body;
     // continuous collision detection only
     const BodyXf *shape_xf;
     const float4 *shape_p;
@@ -226,6 +231,61 @@ __device__ __noinline__ void ccd_pair(const SvArgs &a, uint32_t ia, uint32_t ib,
     if (((mb.x >> 8) & BF_CCD) && cB) test_ccd(a, ib, B, ia, A);
 }
 
+// BradotBody3D::add_contact for the bodies of a contact that asked for contacts (bradot_body_pair_3d.cpp:417-428).  The
+// first `cap` contacts of a body go straight into its records; later ones are parked in the overflow list and merged by
+// k_report_overflow (replace the least deep if deeper), which leaves the N deepest, as the reference's sequential rule does.
+// Impulse: c.acc_impulse after "-= j_vec".  The reference zeroes acc_impulse whenever the contact is regenerated (the new
+// Contact copies the four solver accumulators, not this one: bradot_body_pair_3d.cpp:70-77), so it is -j_vec for a contact
+// refreshed this step and -2 j_vec for one carried from the last step (whose impulses summed to j_vec by then).
+__device__ __noinline__ void report_contact(const SvArgs &a, uint32_t ia, uint32_t ib, const BodyS &A, const BodyS &B, V3 origin_A, V3 gA, V3 gB, V3 rA, V3 rB,
+                                            V3 n, float depth, V3 j_vec, bool refreshed) {
+    uint32_t capA = a.report_cap[ia], capB = a.report_cap[ib];
+    if (!capA && !capB) return;
+    V3 crB = cross(B.ang, rB) + B.lin;
+    V3 crA = cross(A.ang, rA) + A.lin;
+    V3 acc = refreshed ? -j_vec : -j_vec - j_vec;
+    for (int side = 0; side < 2; side++) {
+        uint32_t cap = side ? capB : capA, me = side ? ib : ia;
+        if (!cap) continue;
+        ReportRec r;
+        V3 lp = (side ? gB : gA) + origin_A, ln = side ? n : -n, lv = side ? crB : crA;
+        V3 cp = (side ? gA : gB) + origin_A, cv = side ? crA : crB, im = side ? -acc : acc;
+        r.local_pos[0] = lp.x; r.local_pos[1] = lp.y; r.local_pos[2] = lp.z; r.depth = depth;
+        r.local_normal[0] = ln.x; r.local_normal[1] = ln.y; r.local_normal[2] = ln.z;
+        r.collider = (int32_t)(side ? ia : ib);
+        r.local_velocity[0] = lv.x; r.local_velocity[1] = lv.y; r.local_velocity[2] = lv.z;
+        r.collider_pos[0] = cp.x; r.collider_pos[1] = cp.y; r.collider_pos[2] = cp.z;
+        r.collider_velocity[0] = cv.x; r.collider_velocity[1] = cv.y; r.collider_velocity[2] = cv.z;
+        r.impulse[0] = im.x; r.impulse[1] = im.y; r.impulse[2] = im.z;
+        uint32_t idx = atomicAdd(&a.report_count[me], 1u);
+        if (idx < cap) {
+            a.reports[a.report_ofs[me] + idx] = r;
+        } else {
+            uint32_t o = atomicAdd(&a.counters[CNT_REPORT_OVERFLOW], 1u);
+            if (o < REPORT_OVERFLOW_CAP) {
+                a.report_overflow[o] = r;
+                a.report_overflow_body[o] = me;
+            }
+        }
+    }
+}
+
+// one thread: contacts that arrived after their body's records were full replace the least deep record if they are deeper
+__global__ void k_report_overflow(const uint32_t *__restrict__ counters, const ReportRec *__restrict__ overflow, const uint32_t *__restrict__ overflow_body,
+                                  const uint32_t *__restrict__ cap, const uint32_t *__restrict__ ofs, ReportRec *__restrict__ reports) {
+    if (blockIdx.x || threadIdx.x) return;
+    uint32_t n = min(counters[CNT_REPORT_OVERFLOW], REPORT_OVERFLOW_CAP);
+    for (uint32_t o = 0; o < n; o++) {
+        uint32_t b = overflow_body[o];
+        ReportRec *rec = reports + ofs[b];
+        uint32_t least = 0;
+        for (uint32_t i = 1; i < cap[b]; i++) {
+            if (rec[i].depth < rec[least].depth) least = i;
+        }
+        if (rec[least].depth < overflow[o].depth) rec[least] = overflow[o];
+    }
+}
+
 // pre_solve of one pair; writes SolveContact records at slot s and warm-starts the bodies
 template <bool CCD, bool SH>
 __device__ inline void pre_solve_pair(const SvArgs &a, const ShBodies &sb, uint32_t s, uint32_t k) {
@@ -288,6 +348,14 @@ __device__ inline void pre_solve_pair(const SvArgs &a, const ShBodies &sb, uint3
         float mass_normal = 1.0f / kN;
         float cbias = -bias * a.inv_dt * fminf(0.0f, -depth + max_pen);
         V3 j_vec = n * ac.t_n.w + f4v(ac.t_n);
+        if (a.report_cap) report_contact(a, ia, ib, A, B, f4v(xa.o), gA, gB, rA, rB, n, depth, j_vec, (__float_as_uint(g.la.w) & 1u) != 0);
+        if (!cA && !cB) { // a pair kept only for its contact report (report_contacts_only, bradot_body_pair_3d.cpp:275-283, 430-433)
+            sc.n_mn = v4(n, 0.f);
+            sc.ra_b = make_float4(0.f, 0.f, 0.f, 0.f);
+            sc.rb_bo = make_float4(0.f, 0.f, 0.f, 0.f);
+            a.sc[(size_t)c * a.sc_stride + s] = sc;
+            continue;
+        }
         if (cA) apply_impulse(A, -j_vec, rA + A.com);
         if (cB) apply_impulse(B, j_vec, rB + B.com);
         float bounce = cb;
@@ -948,6 +1016,12 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     a.sc_stride = maxc;
     a.joints = ctx->d_joints.p;
     a.jsetup = ctx->jsetup.p;
+    a.report_cap = ctx->n_reporting ? ctx->report_cap.p : nullptr;
+    a.report_ofs = ctx->report_ofs.p;
+    a.report_count = ctx->report_count.p;
+    a.reports = ctx->reports.p;
+    a.report_overflow = ctx->report_overflow.p;
+    a.report_overflow_body = ctx->report_overflow_body.p;
     a.shape_xf = ctx->shape_xf.p;
     a.shape_p = ctx->shape_p.p;
     a.medges = ctx->medges.p;
@@ -984,6 +1058,12 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
             attr_set = true;
         }
         k_solve_bins<<<ctx->n_bins, SB_THREADS, smem, st>>>(a);
+        BPC_CHECK(cudaGetLastError());
+        ctx->launches += 1;
+    }
+    if (ctx->n_reporting) {
+        k_report_overflow<<<1, 32, 0, st>>>(ctx->counters.p, ctx->report_overflow.p, ctx->report_overflow_body.p, ctx->report_cap.p, ctx->report_ofs.p,
+                                            ctx->reports.p);
         BPC_CHECK(cudaGetLastError());
         ctx->launches += 1;
     }

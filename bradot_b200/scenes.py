@@ -34,7 +34,8 @@ PIN_DEFAULTS = np.array([0.3, 1.0, 0.0, 0, 0, 0, 0, 0], np.float32)
 HINGE_DEFAULTS = np.array([0.3, -np.pi, np.pi, 0.3, 0.9, 1.0, 0.0, 0.0], np.float32)   # upper = -pi, lower = pi: the reference's "no limit"
 # body flags: bit0 can_sleep, bit1 continuous cd, bit2 start asleep, bit3 pushed every step, bit4 / bit5 linear / angular damp
 # mode REPLACE, bits 8..13 axis locks (PhysicsServer3D::BodyAxis: linear x y z, angular x y z)
-BODY_LIN_DAMP_REPLACE, BODY_ANG_DAMP_REPLACE, BODY_LOCK_SHIFT = 16, 32, 8
+# bits 16..23: body_set_max_contacts_reported
+BODY_LIN_DAMP_REPLACE, BODY_ANG_DAMP_REPLACE, BODY_LOCK_SHIFT, BODY_REPORT_SHIFT = 16, 32, 8, 16
 IDENT12 = np.array([1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0], dtype=np.float32)
 
 

@@ -43,6 +43,7 @@ EXPORTS = [
     "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
     "bpc_bodies_set_state", "bpc_bodies_read_slots", "bpc_bodies_write_slots", "bpc_bodies_read_state", "bpc_reserve",
     "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_test_segment_math", "bpc_bodies_set_exception",
+    "bpc_bodies_set_max_contacts_reported", "bpc_body_read_contacts", "bpc_contacts_capacity", "bpc_contacts_read",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
@@ -58,6 +59,8 @@ class PhysicsError(RuntimeError):
     pass
 
 
+CONTACT_DT = np.dtype([("local_pos", "<f4", 3), ("depth", "<f4"), ("local_normal", "<f4", 3), ("collider", "<i4"), ("local_velocity", "<f4", 3),
+                       ("collider_pos", "<f4", 3), ("collider_velocity", "<f4", 3), ("impulse", "<f4", 3)])
 RAY_RESULT_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("position", "<f4", 3), ("normal", "<f4", 3)])
 
 
@@ -97,6 +100,10 @@ def load_library(path=LIB_PATH):
     lib.bpc_bodies_read_state.argtypes = [vp, ci, ci, vp]
     lib.bpc_reserve.argtypes = [vp, ci, ci]
     lib.bpc_bodies_set_exception.argtypes = [vp, ci, ci, ci]
+    lib.bpc_bodies_set_max_contacts_reported.argtypes = [vp, vp, ci, vp]
+    lib.bpc_body_read_contacts.argtypes = [vp, ci, ci, vp]
+    lib.bpc_contacts_capacity.argtypes = [vp]
+    lib.bpc_contacts_read.argtypes = [vp, vp, vp, vp]
     lib.bpc_test_segment_math.argtypes = [vp, ci, ci, vp, vp]
     lib.bpc_step.argtypes = [vp, cf]
     lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
@@ -264,6 +271,26 @@ class PhysicsServerCUDA:
     def body_set_collision_exception(self, a, b, excepted=True):
         self._check(self.lib.bpc_bodies_set_exception(self.ctx, int(a), int(b), 1 if excepted else 0))
 
+    def bodies_set_max_contacts_reported(self, slots, counts):
+        sl = np.ascontiguousarray(slots, np.int32).reshape(-1)
+        c = np.ascontiguousarray(counts, np.int32).reshape(-1)
+        self._check(self.lib.bpc_bodies_set_max_contacts_reported(self.ctx, _ptr(sl), len(sl), _ptr(c)))
+
+    def body_contacts(self, slot, max_records=64):
+        """Contacts reported to one body in the last step (structured array, CONTACT_DT)."""
+        out = np.zeros(max_records, CONTACT_DT)
+        n = self._check(self.lib.bpc_body_read_contacts(self.ctx, int(slot), max_records, _ptr(out)))
+        return out[:min(n, max_records)]
+
+    def contacts_read(self):
+        """(counts, offsets, records) of every body's reported contacts in one copy."""
+        n = self.body_count()
+        cap = self._check(self.lib.bpc_contacts_capacity(self.ctx))
+        counts, offsets = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        rec = np.zeros(max(cap, 1), CONTACT_DT)
+        self._check(self.lib.bpc_contacts_read(self.ctx, _ptr(counts), _ptr(offsets), _ptr(rec)))
+        return counts, offsets, rec[:cap]
+
     def reserve(self, bodies, pairs):
         self._check(self.lib.bpc_reserve(self.ctx, int(bodies), int(pairs)))
 
@@ -400,6 +427,10 @@ class PhysicsServerCUDA:
             bodies["linvel"][kin] = 0
             bodies["angvel"][kin] = 0
         first = self.bodies_create(bodies) if len(bodies) else 0
+        want = (bodies["flags"] >> scenes.BODY_REPORT_SHIFT) & 0xFF     # body_set_max_contacts_reported
+        if want.any():
+            idx = np.nonzero(want)[0]
+            self.bodies_set_max_contacts_reported(first + idx, want[idx])
         if len(sc.joints):
             self.joints_create(sc.joints)
         return first

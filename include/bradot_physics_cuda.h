@@ -167,6 +167,26 @@ int bpc_bodies_read_state(bpc_context *ctx, int first, int n, float *host);
  * add theirs on their own). */
 int bpc_bodies_set_exception(bpc_context *ctx, int body_a, int body_b, int excepted);
 
+/* Contact reporting: body_set_max_contacts_reported + the PhysicsDirectBodyState3D contact getters
+ * (P3D/bradot_body_3d.h:353-395, P3D/bradot_body_pair_3d.cpp:417-428).  A body that asks for up to N contacts gets, each
+ * step, the N deepest contacts it takes part in (the reference keeps the N deepest too; their order in the list is not
+ * defined here).  Positions and velocities are world-space as the reference reports them; `impulse` is the contact's
+ * accumulated impulse at pre-solve time; `collider` is the other body's index.  A pair none of whose bodies would otherwise
+ * collide (static against kinematic) is still tested when one of them reports contacts, as in the reference. */
+typedef struct bpc_contact {
+    float local_pos[3], depth;
+    float local_normal[3];
+    int32_t collider;
+    float local_velocity[3], collider_pos[3], collider_velocity[3], impulse[3];
+} bpc_contact;
+int bpc_bodies_set_max_contacts_reported(bpc_context *ctx, const int32_t *slots, int n, const int32_t *max_contacts);
+/* Contacts of one body from the last step: at most max_records are written, the number available is returned. */
+int bpc_body_read_contacts(bpc_context *ctx, int slot, int max_records, bpc_contact *out);
+/* All reported contacts of the last step in one copy: counts[n_bodies] (contacts of each body), offsets[n_bodies] (where its
+ * records start in `records`), records[bpc_contacts_capacity()]. */
+int bpc_contacts_capacity(bpc_context *ctx);
+int bpc_contacts_read(bpc_context *ctx, int32_t *counts, int32_t *offsets, bpc_contact *records);
+
 /* Size every per-body and per-pair buffer for `bodies` bodies and `pairs` broadphase pairs up front, so that bpc_step does
  * not allocate while the counts stay below them (a pair burst beyond `pairs` still grows the buffers, once). */
 int bpc_reserve(bpc_context *ctx, int bodies, int pairs);

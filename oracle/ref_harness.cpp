@@ -82,7 +82,8 @@ struct ScnShape {
 };
 struct ScnBody {
 	// flags bit0 can_sleep, bit1 ccd, bit2 start asleep, bit3 pushed every step (see push_bodies),
-	// bit4 / bit5 linear / angular damp mode REPLACE, bits 8..13 axis locks (PhysicsServer3D::BodyAxis)
+	// bit4 / bit5 linear / angular damp mode REPLACE, bits 8..13 axis locks (PhysicsServer3D::BodyAxis),
+	// bits 16..23 body_set_max_contacts_reported
 	uint32_t space, mode, shape, flags;
 	float xf[12]; // basis rows (9) + origin
 	float shape_xf[12];
@@ -245,6 +246,37 @@ static void dump_step(Dump &d, World &w, int step) {
 		items.push_back((float)id);
 	}
 	d.arr("bodies", step, "f4", { (uint64_t)nb, 20 }, bs.data(), bs.size() * 4);
+	// contacts reported to the bodies that asked for them (BradotBody3D::contacts, filled by add_contact in pre_solve):
+	// body, local_pos(3), local_normal(3), depth, local_velocity(3), collider_pos(3), collider body, collider_velocity(3), impulse(3)
+	{
+		std::map<RID, int> rid_index;
+		for (int i = 0; i < nb; i++) {
+			rid_index[w.bodies[i]] = i;
+		}
+		std::vector<float> rep;
+		for (int i = 0; i < nb; i++) {
+			if (w.body_freed[i]) {
+				continue;
+			}
+			BradotBody3D *b = w.body_ptr[i];
+			for (int k = 0; k < b->contact_count; k++) {
+				const BradotBody3D::Contact &c = b->contacts[k];
+				rep.push_back((float)i);
+				put3(rep, c.local_pos);
+				put3(rep, c.local_normal);
+				rep.push_back(c.depth);
+				put3(rep, c.local_velocity_at_pos);
+				put3(rep, c.collider_pos);
+				auto it = rid_index.find(c.collider);
+				rep.push_back(it == rid_index.end() ? -1.f : (float)it->second);
+				put3(rep, c.collider_velocity_at_pos);
+				put3(rep, c.impulse);
+			}
+		}
+		if (!rep.empty()) {
+			d.arr("reports", step, "f4", { (uint64_t)rep.size() / 21, 21 }, rep.data(), rep.size() * 4);
+		}
+	}
 	d.arr("items", step, "f4", { (uint64_t)nb, 14 }, items.data(), items.size() * 4);
 
 	// pairs: walk constraint maps, emit each BradotBodyPair3D once (from its A side)
@@ -729,6 +761,9 @@ int main(int argc, char **argv) {
 			if ((b.flags >> 8) & (1u << ax)) {
 				ps->body_set_axis_lock(body, (PhysicsServer3D::BodyAxis)(1 << ax), true);
 			}
+		}
+		if ((b.flags >> 16) & 0xff) {
+			ps->body_set_max_contacts_reported(body, (b.flags >> 16) & 0xff);
 		}
 		ps->body_set_space(body, w.spaces[b.space]);
 		if (b.flags & 4) {
