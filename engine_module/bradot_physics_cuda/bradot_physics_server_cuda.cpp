@@ -388,6 +388,8 @@ void BradotPhysicsServerCUDA::_body_leave_space(Body *p_body) {
 		body_of_slot[slot] = nullptr;
 		p_body->slot = -1;
 		state_cache_valid = false;
+		contact_cache_valid = false;
+		single_contacts_slot = -1;
 	}
 }
 
@@ -717,6 +719,50 @@ bool BradotPhysicsServerCUDA::body_is_axis_locked(RID p_body, BodyAxis p_axis) c
 	return body->locked_axis & (uint32_t)p_axis;
 }
 
+// body_set_max_contacts_reported (bradot_physics_server_3d.cpp:819-824; BradotBody3D::set_max_contacts_reported resizes the
+// body's contact list): the body's table of the N deepest contacts on the GPU
+void BradotPhysicsServerCUDA::body_set_max_contacts_reported(RID p_body, int p_contacts) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	ERR_FAIL_COND(p_contacts < 0);
+	reporting_bodies += (p_contacts > 0 ? 1 : 0) - (body->max_contacts_reported > 0 ? 1 : 0);
+	body->max_contacts_reported = p_contacts;
+	if (body->slot >= 0) {
+		int32_t slot = body->slot, cap = p_contacts;
+		ERR_FAIL_COND_MSG(bpc_bodies_set_max_contacts_reported(ctx, &slot, 1, &cap) < 0, bpc_last_error(ctx));
+		contact_cache_valid = false;
+		single_contacts_slot = -1;
+	}
+}
+
+int BradotPhysicsServerCUDA::body_get_max_contacts_reported(RID p_body) const {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, -1);
+	return body->max_contacts_reported;
+}
+
+// The contacts reported to one body in the last step: from the bulk copy of flush_queries() when there is one, else read
+// for this body alone (and kept until the next step or the next body asked about).
+const bpc_contact *BradotPhysicsServerCUDA::_body_contacts(const Body *p_body, int &r_count) {
+	r_count = 0;
+	if (p_body->slot < 0 || p_body->max_contacts_reported <= 0) {
+		return nullptr;
+	}
+	if (contact_cache_valid && (uint32_t)p_body->slot < contact_counts.size()) {
+		r_count = contact_counts[p_body->slot];
+		return contact_records.ptr() + contact_offsets[p_body->slot];
+	}
+	if (single_contacts_slot != p_body->slot) {
+		single_contacts.resize(p_body->max_contacts_reported);
+		int n = bpc_body_read_contacts(ctx, p_body->slot, p_body->max_contacts_reported, single_contacts.ptr());
+		ERR_FAIL_COND_V_MSG(n < 0, nullptr, bpc_last_error(ctx));
+		single_contacts_slot = p_body->slot;
+		single_contacts_count = MIN(n, p_body->max_contacts_reported);
+	}
+	r_count = single_contacts_count;
+	return single_contacts.ptr();
+}
+
 void BradotPhysicsServerCUDA::body_set_omit_force_integration(RID p_body, bool p_omit) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
@@ -995,6 +1041,54 @@ void BradotPhysicsServerCUDA::_body_call_queries(Body *p_body) {
 #define DIRECT_BODY(m_ret)                                                \
 	BradotPhysicsServerCUDA::Body *b = server->body_owner.get_or_null(body); \
 	ERR_FAIL_NULL_V(b, m_ret);
+
+#define DIRECT_CONTACT(m_ret)                                   \
+	DIRECT_BODY(m_ret);                                         \
+	int contact_count = 0;                                      \
+	const bpc_contact *c = server->_body_contacts(b, contact_count); \
+	ERR_FAIL_INDEX_V(p_contact_idx, contact_count, m_ret);      \
+	c += p_contact_idx;
+
+int BradotPhysicsDirectBodyStateCUDA::get_contact_count() const {
+	DIRECT_BODY(0);
+	int contact_count = 0;
+	server->_body_contacts(b, contact_count);
+	return contact_count;
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_contact_local_position(int p_contact_idx) const {
+	DIRECT_CONTACT(Vector3());
+	return Vector3(c->local_pos[0], c->local_pos[1], c->local_pos[2]);
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_contact_local_normal(int p_contact_idx) const {
+	DIRECT_CONTACT(Vector3());
+	return Vector3(c->local_normal[0], c->local_normal[1], c->local_normal[2]);
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_contact_impulse(int p_contact_idx) const {
+	DIRECT_CONTACT(Vector3());
+	return Vector3(c->impulse[0], c->impulse[1], c->impulse[2]);
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_contact_local_velocity_at_position(int p_contact_idx) const {
+	DIRECT_CONTACT(Vector3());
+	return Vector3(c->local_velocity[0], c->local_velocity[1], c->local_velocity[2]);
+}
+RID BradotPhysicsDirectBodyStateCUDA::get_contact_collider(int p_contact_idx) const {
+	DIRECT_CONTACT(RID());
+	BradotPhysicsServerCUDA::Body *o = (uint32_t)c->collider < server->body_of_slot.size() ? server->body_of_slot[c->collider] : nullptr;
+	return o ? o->self : RID();
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_contact_collider_position(int p_contact_idx) const {
+	DIRECT_CONTACT(Vector3());
+	return Vector3(c->collider_pos[0], c->collider_pos[1], c->collider_pos[2]);
+}
+ObjectID BradotPhysicsDirectBodyStateCUDA::get_contact_collider_id(int p_contact_idx) const {
+	DIRECT_CONTACT(ObjectID());
+	BradotPhysicsServerCUDA::Body *o = (uint32_t)c->collider < server->body_of_slot.size() ? server->body_of_slot[c->collider] : nullptr;
+	return o ? o->instance_id : ObjectID();
+}
+Vector3 BradotPhysicsDirectBodyStateCUDA::get_contact_collider_velocity_at_position(int p_contact_idx) const {
+	DIRECT_CONTACT(Vector3());
+	return Vector3(c->collider_velocity[0], c->collider_velocity[1], c->collider_velocity[2]);
+}
 
 Vector3 BradotPhysicsDirectBodyStateCUDA::get_total_gravity() const {
 	DIRECT_BODY(Vector3());
@@ -1302,6 +1396,7 @@ void BradotPhysicsServerCUDA::free(RID p_rid) {
 		memdelete(s);
 	} else if (body_owner.owns(p_rid)) {
 		Body *b = body_owner.get_or_null(p_rid);
+		reporting_bodies -= b->max_contacts_reported > 0 ? 1 : 0;
 		_body_leave_space(b);
 		if (b->pushed) {
 			pushed_bodies.erase(b);
@@ -1400,6 +1495,10 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 				if (b->constant_force != Vector3() || b->constant_torque != Vector3()) {
 					_write_constant(ctx, b->slot, b->constant_force, b->constant_torque);
 				}
+				if (b->max_contacts_reported > 0) {
+					int32_t slot = b->slot, cap = b->max_contacts_reported;
+					bpc_bodies_set_max_contacts_reported(ctx, &slot, 1, &cap);
+				}
 			}
 			// exceptions named before both bodies were in a space
 			for (Body *b : uploaded) {
@@ -1491,6 +1590,8 @@ void BradotPhysicsServerCUDA::step(real_t p_step) {
 	last_step = p_step;
 	stepped_since_flush = true;
 	state_cache_valid = false;
+	contact_cache_valid = false;
+	single_contacts_slot = -1;
 	ERR_FAIL_COND_MSG(bpc_step(ctx, p_step) < 0, bpc_last_error(ctx));
 }
 
@@ -1521,6 +1622,12 @@ void BradotPhysicsServerCUDA::flush_queries() {
 			ERR_FAIL_MSG(bpc_last_error(ctx));
 		}
 		state_cache_valid = true;
+		if (reporting_bodies > 0) {
+			contact_counts.resize(n);
+			contact_offsets.resize(n);
+			contact_records.resize(MAX(1, bpc_contacts_capacity(ctx)));
+			contact_cache_valid = bpc_contacts_read(ctx, contact_counts.ptr(), contact_offsets.ptr(), contact_records.ptr()) >= 0;
+		}
 		uint32_t old = was_active.size();
 		was_active.resize(n);
 		for (uint32_t i = old; i < (uint32_t)n; i++) {

@@ -84,18 +84,18 @@ public:
 	virtual Vector3 get_constant_torque() const override;
 	virtual void set_sleep_state(bool p_sleep) override;
 	virtual bool is_sleeping() const override;
-	// contact reporting is a "next" row: a body reports no contacts
-	virtual int get_contact_count() const override { return 0; }
-	virtual Vector3 get_contact_local_position(int p_contact_idx) const override { return Vector3(); }
-	virtual Vector3 get_contact_local_normal(int p_contact_idx) const override { return Vector3(); }
-	virtual Vector3 get_contact_impulse(int p_contact_idx) const override { return Vector3(); }
-	virtual int get_contact_local_shape(int p_contact_idx) const override { return 0; }
-	virtual Vector3 get_contact_local_velocity_at_position(int p_contact_idx) const override { return Vector3(); }
-	virtual RID get_contact_collider(int p_contact_idx) const override { return RID(); }
-	virtual Vector3 get_contact_collider_position(int p_contact_idx) const override { return Vector3(); }
-	virtual ObjectID get_contact_collider_id(int p_contact_idx) const override { return ObjectID(); }
+	// the contacts BradotBody3D::add_contact kept for this body in the last step (bradot_body_direct_state_3d.cpp:205-262)
+	virtual int get_contact_count() const override;
+	virtual Vector3 get_contact_local_position(int p_contact_idx) const override;
+	virtual Vector3 get_contact_local_normal(int p_contact_idx) const override;
+	virtual Vector3 get_contact_impulse(int p_contact_idx) const override;
+	virtual int get_contact_local_shape(int p_contact_idx) const override { return 0; } // one shape per body
+	virtual Vector3 get_contact_local_velocity_at_position(int p_contact_idx) const override;
+	virtual RID get_contact_collider(int p_contact_idx) const override;
+	virtual Vector3 get_contact_collider_position(int p_contact_idx) const override;
+	virtual ObjectID get_contact_collider_id(int p_contact_idx) const override;
 	virtual int get_contact_collider_shape(int p_contact_idx) const override { return 0; }
-	virtual Vector3 get_contact_collider_velocity_at_position(int p_contact_idx) const override { return Vector3(); }
+	virtual Vector3 get_contact_collider_velocity_at_position(int p_contact_idx) const override;
 	virtual real_t get_step() const override;
 	virtual PhysicsDirectSpaceState3D *get_space_state() override;
 };
@@ -129,6 +129,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		bool omit_force_integration = false;
 		bool lin_damp_replace = false, ang_damp_replace = false;
 		uint32_t locked_axis = 0;
+		int max_contacts_reported = 0;
 		ObjectID instance_id;
 		Vector3 applied_force, applied_torque; // accumulated by body_apply_*, handed over in one write before the next step
 		Vector3 constant_force, constant_torque;
@@ -180,6 +181,13 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	LocalVector<float> state_cache;
 	LocalVector<uint8_t> was_active; // active flag per slot one tick earlier
 	bool state_cache_valid = false;
+	// reported contacts of the last tick: all bodies in ONE copy at flush_queries() when anybody has a callback, else the
+	// one body asked about (single_contacts)
+	LocalVector<int32_t> contact_counts, contact_offsets;
+	LocalVector<bpc_contact> contact_records, single_contacts;
+	bool contact_cache_valid = false;
+	int single_contacts_slot = -1, single_contacts_count = 0;
+	int reporting_bodies = 0;
 	bpc_stats last_stats = {};
 
 	int _shape_handle(Shape *p_shape);
@@ -193,6 +201,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	void _body_call_queries(Body *p_body);
 	void _body_push(Body *p_body);
 	const float *_body_cached_state(const Body *p_body);
+	const bpc_contact *_body_contacts(const Body *p_body, int &r_count);
 	bool _body_mass_world(const Body *p_body, Basis &r_iinv, Vector3 &r_com, real_t &r_inv_mass) const;
 
 protected:
@@ -261,6 +270,8 @@ public:
 	virtual void body_add_collision_exception(RID p_body, RID p_body_b) override;
 	virtual void body_remove_collision_exception(RID p_body, RID p_body_b) override;
 	virtual void body_get_collision_exceptions(RID p_body, List<RID> *p_exceptions) override;
+	virtual void body_set_max_contacts_reported(RID p_body, int p_contacts) override;
+	virtual int body_get_max_contacts_reported(RID p_body) const override;
 	virtual void body_set_omit_force_integration(RID p_body, bool p_omit) override;
 	virtual bool body_is_omitting_force_integration(RID p_body) const override;
 	virtual void body_set_state_sync_callback(RID p_body, const Callable &p_callable) override;

@@ -44,11 +44,19 @@ struct Event { int32_t step, body, kind; float v[12]; };
 // what the state-sync callbacks reported: last transform per body, number of calls
 static std::vector<Transform3D> g_synced;
 static std::vector<int> g_sync_calls;
+// ... and the contacts its direct state listed at that call (bodies with max_contacts_reported > 0)
+struct SeenContact { RID collider; ObjectID collider_id; Vector3 pos, normal, impulse, vel, collider_pos, collider_vel; };
+static std::vector<std::vector<SeenContact>> g_contacts;
 static void on_state_sync(Object *p_state, int p_index) {
 	PhysicsDirectBodyState3D *st = Object::cast_to<PhysicsDirectBodyState3D>(p_state);
 	if (st && p_index >= 0 && p_index < (int)g_synced.size()) {
 		g_synced[p_index] = st->get_transform();
 		g_sync_calls[p_index]++;
+		g_contacts[p_index].clear();
+		for (int i = 0; i < st->get_contact_count(); i++) {
+			g_contacts[p_index].push_back({ st->get_contact_collider(i), st->get_contact_collider_id(i), st->get_contact_local_position(i), st->get_contact_local_normal(i),
+					st->get_contact_impulse(i), st->get_contact_local_velocity_at_position(i), st->get_contact_collider_position(i), st->get_contact_collider_velocity_at_position(i) });
+		}
 	}
 }
 
@@ -189,11 +197,16 @@ int main(int argc, char **argv) {
 				ps->body_set_axis_lock(body, (PhysicsServer3D::BodyAxis)(1 << ax), true);
 			}
 		}
+		if ((b.flags >> 16) & 0xFF) {
+			ps->body_set_max_contacts_reported(body, (b.flags >> 16) & 0xFF);
+		}
+		ps->body_attach_object_instance_id(body, ObjectID((uint64_t)(1000 + body_r.size())));
 		ps->body_set_space(body, space_r[b.space]);
 		ps->body_set_state_sync_callback(body, callable_mp_static(&on_state_sync).bind((int)body_r.size()));
 		body_r.push_back(body);
 	}
 	g_synced.resize(body_r.size());
+	g_contacts.resize(body_r.size());
 	g_sync_calls.assign(body_r.size(), 0);
 	std::vector<char> freed(body_r.size(), 0);
 	// scene flag bit3: pushed before every step, the same push as oracle/ref_harness.cpp push_bodies()
@@ -277,6 +290,27 @@ int main(int argc, char **argv) {
 	printf("], \"sleeping\": [");
 	for (size_t i = 0; i < body_r.size(); i++) {
 		printf("%s%d", i ? ", " : "", freed[i] ? -1 : (int)(bool)ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_SLEEPING));
+	}
+	printf("], \"contacts\": [");
+	for (size_t i = 0; i < body_r.size(); i++) { // per body: [collider index, collider object id, 18 floats] of every contact last listed
+		printf("%s[", i ? ", " : "");
+		for (size_t k = 0; k < g_contacts[i].size(); k++) {
+			const SeenContact &c = g_contacts[i][k];
+			int idx = -1;
+			for (size_t q = 0; q < body_r.size(); q++) {
+				if (body_r[q] == c.collider) {
+					idx = (int)q;
+					break;
+				}
+			}
+			const Vector3 *v[6] = { &c.pos, &c.normal, &c.impulse, &c.vel, &c.collider_pos, &c.collider_vel };
+			printf("%s[%d, %lld", k ? ", " : "", idx, (long long)(uint64_t)c.collider_id);
+			for (int q = 0; q < 6; q++) {
+				printf(", %.9g, %.9g, %.9g", v[q]->x, v[q]->y, v[q]->z);
+			}
+			printf("]");
+		}
+		printf("]");
 	}
 	printf("], \"rays\": [");
 	// PhysicsDirectSpaceState3D::intersect_ray through the RID API: straight down onto the first bodies

@@ -124,7 +124,10 @@ def test_full_size_c2_pair_list_and_manifold_properties():
     assert np.all(ids[col, 2] >= 1) and np.all(ids[:, 2] <= 4)
     valid = np.arange(4)[None, :] < ids[:, 2][:, None]
     n = cf[:, :, 6:9][valid]
-    assert np.allclose(np.linalg.norm(n, axis=1), 1.0, atol=1e-5)
+    # (a contact whose two points coincide gets the zero vector: (p_point_A - p_point_B).normalized(), bradot_body_pair_3d.cpp:60;
+    # its depth is 0 and the solver skips it.  In 336k contacts that happens once or not at all.)
+    nn = np.linalg.norm(n, axis=1)
+    assert np.all((np.abs(nn - 1.0) < 1e-5) | (nn == 0.0)) and int((nn == 0.0).sum()) <= 3
     assert np.all(np.isfinite(cf)) and np.all(cf[:, :, 9][valid] >= 0)
     xf = ps.bodies_read(server.FIELD_TRANSFORM)
     dyn = ~static

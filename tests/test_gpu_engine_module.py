@@ -127,3 +127,43 @@ def test_engine_module_callbacks_set_state_and_free_match_c_abi_and_reference(tm
     assert np.array_equal(synced[alive & dyn, 1:4].astype(np.float32), engine[alive & dyn])
     # a body asleep for most of the run was told far fewer times than there were ticks
     assert calls[4] < steps // 2
+
+
+def test_engine_module_reported_contacts_match_direct_c_abi(tmp_path):
+    """body_set_max_contacts_reported + the PhysicsDirectBodyState3D contact getters through the RID API (read inside the
+    state-sync callbacks, as RigidBody3D does for its body_entered signals: scene/3d/physics/rigid_body_3d.cpp:455-520)
+    against bpc_contacts_read on the same scene: the same records, the collider mapped back to its RID and object id."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    sc = scenes.pyramid(36, base=8)
+    flags = sc.bodies["flags"].copy()
+    flags[1:] |= np.where(np.arange(len(flags) - 1) % 2 == 0, 6, 0).astype(np.uint32) << scenes.BODY_REPORT_SHIFT
+    flags[10] = (flags[10] & 0xFF00FFFF) | (2 << scenes.BODY_REPORT_SHIFT)
+    sc.bodies["flags"] = flags
+    path = str(tmp_path / "scene.bscn")
+    sc.write(path)
+    steps = 20
+    r = subprocess.run([DEMO, path, str(steps)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc)
+    for _ in range(steps):
+        ps.step(sc.dt)
+    counts, offsets, rec = ps.contacts_read()
+    ps.finish()
+    seen = 0
+    for body, listed in enumerate(out["contacts"]):
+        mine = rec[offsets[body]:offsets[body] + counts[body]]
+        assert len(listed) == len(mine), body
+        if not len(mine):
+            continue
+        got = np.array(listed, np.float64)
+        assert np.all(got[:, 1] == got[:, 0] + 1000)          # collider object id = what the demo attached to that body
+        want = np.concatenate([mine["collider"][:, None].astype(np.float64), mine["local_pos"], mine["local_normal"], mine["impulse"],
+                               mine["local_velocity"], mine["collider_pos"], mine["collider_velocity"]], axis=1)
+        got = np.delete(got, 1, axis=1)
+        o1, o2 = np.lexsort(got.T[::-1]), np.lexsort(want.T[::-1])
+        assert np.array_equal(got[o1].astype(np.float32), want[o2].astype(np.float32)), body
+        seen += len(mine)
+    assert seen > 40
