@@ -124,6 +124,25 @@ struct SpaceParams {
 #define BIN_BLOCK 256u
 #define BIN_MAX_BODIES 704u
 #define BIN_MAX_CONS 2048u
+
+// The exclude list of the space queries (ShapeParameters::exclude and friends, bradot_space_3d.cpp:86,151,233,294,408,540):
+// sorted body indices, looked up per candidate.
+struct QExclude {
+    const uint32_t *ids;
+    uint32_t n;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ bool q_excluded(const QExclude &e, uint32_t body) {
+    uint32_t lo = 0, hi = e.n;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (e.ids[mid] < body) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo < e.n && e.ids[lo] == body;
+}
+#endif
+
 #endif
 
 // stages timed by bpc_set_profiling: forces, broadphase, islands, narrowphase, schedule, solve, integrate+sleep
@@ -193,6 +212,8 @@ struct bpc_context {
     DevBuf<uint32_t> a_range; // [2 * n_bodies]: begin / end of each body's run (as A) in the previous pair list
     DevBuf<uint32_t> io_slots; // body indices of a gather / scatter call
     DevBuf<float> staging;    // packed per-body floats on their way to / from the host (bulk state I/O)
+    DevBuf<uint32_t> q_exclude; // bodies the space queries skip (bpc_space_set_query_exclude), sorted
+    uint32_t n_q_exclude = 0;
     DevBuf<uint32_t> np_work; // broadphase pairs that need the full narrowphase pass this step
     DevBuf<uint32_t> np_cwork; // hull-against-hull pairs handed to the warp-per-pair kernel
     DevBuf<uint64_t> forced_keys;

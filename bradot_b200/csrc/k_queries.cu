@@ -10,6 +10,8 @@
 // answer is the hit of least `normal . point`.  Candidates only have to be a superset of the shapes the segment really
 // meets, so any conservative segment/box test over OUR tree gives the same answer (except for exact ties, which the
 // reference breaks by its own tree order).
+#include <algorithm>
+#include <vector>
 #include "../../include/bradot_physics_cuda.h"
 #include "np_segment.cuh"
 
@@ -30,6 +32,7 @@ struct QArgs {
     MeshPools pools;
     const uint32_t *big;
     const uint32_t *big_start;
+    QExclude ex;
 };
 
 struct RayBest {
@@ -44,6 +47,7 @@ __device__ inline bool q_ray_candidate(const QArgs &a, uint32_t j, V3 begin, V3 
     uint4 m = a.meta[j];
     if (m.w != a.space) return false;
     if (!(m.y & a.mask)) return false; // _can_collide_with: layer & mask (bodies only exist here)
+    if (a.ex.n && q_excluded(a.ex, j)) return false;
     BodyXf bx = a.xf[j];
     X3 xf(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
     // get_inv_transform(): Transform3D::inverse() once a step has moved the body (bradot_body_3d.cpp:735),
@@ -166,6 +170,7 @@ __device__ inline void q_point_candidate(const PArgs &a, uint32_t j, V3 point, u
     if (cc >= (int)a.max_results) return;
     uint4 m = a.q.meta[j];
     if (m.w != a.q.space || !(m.y & a.q.mask)) return;
+    if (a.q.ex.n && q_excluded(a.q.ex, j)) return;
     BodyXf bx = a.q.xf[j];
     X3 xf(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
     if (!((m.x >> 8) & BF_SHAPE_IDENT)) {
@@ -243,6 +248,41 @@ static void q_fill(bpc_context *ctx, QArgs &a, int space, int n, unsigned mask, 
     a.pools.mindex = ctx->mindex.p;
     a.big = ctx->big_items.p;
     a.big_start = ctx->big_start.p;
+    a.ex.ids = ctx->q_exclude.p;
+    a.ex.n = ctx->n_q_exclude;
+}
+
+// ShapeParameters / RayParameters / PointParameters ::exclude (servers/physics_server_3d.h:139-201): the bodies every query of
+// this context skips from now on; n = 0 clears the list.
+extern "C" int bpc_space_set_query_exclude(bpc_context *ctx, const int32_t *bodies, int n) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && !bodies)) {
+        ctx->err = "bpc_space_set_query_exclude: bad arguments";
+        return -1;
+    }
+    std::vector<uint32_t> ids;
+    for (int i = 0; i < n; i++) {
+        if (bodies[i] < 0 || (uint32_t)bodies[i] >= ctx->n_bodies) {
+            ctx->err = "bpc_space_set_query_exclude: no such body";
+            return -1;
+        }
+        ids.push_back((uint32_t)bodies[i]);
+    }
+    std::sort(ids.begin(), ids.end());
+    ids.erase(std::unique(ids.begin(), ids.end()), ids.end());
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    ctx->n_q_exclude = 0;
+    if (!ids.empty()) {
+        ctx->q_exclude.reserve(ids.size(), false, ctx->stream);
+        if (!ctx->q_exclude.p) {
+            ctx->err = "bpc_space_set_query_exclude: out of device memory";
+            return -1;
+        }
+        BPC_CHECK(cudaMemcpyAsync(ctx->q_exclude.p, ids.data(), ids.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        BPC_CHECK(cudaStreamSynchronize(ctx->stream)); // `ids` goes out of scope
+        ctx->n_q_exclude = (uint32_t)ids.size();
+    }
+    return 0;
 }
 
 extern "C" int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int max_results,

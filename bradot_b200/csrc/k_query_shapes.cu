@@ -4,7 +4,10 @@
 // The candidates come from the LBVH by box overlap with the query shape's world AABB (a superset of the reference's
 // cull: its BVH holds the same stored boxes); the decision is the narrowphase routine in TEST mode, exactly what the
 // reference runs when no result callback is given.  Margin 0 only (the reference's withMargin variants are not built).
+#include <string>
+
 #include "../../include/bradot_physics_cuda.h"
+#include "np_gjk.cuh"
 #include "np_sat.cuh"
 
 int bpc_flush_tables(bpc_context *ctx); // bpc_bodies.cu: shape / mesh tables to the device
@@ -33,6 +36,14 @@ struct QsArgs {
     const uint32_t *mindex;
     const uint32_t *big;
     const uint32_t *big_start;
+    QExclude ex;
+    // rest_info / cast_motion
+    const float *motions; // n x 3 (may be null: no motion)
+    float margin;
+    const BodyVel *vel;
+    const BodyMassW *massw;
+    bpc_rest_info *rest_out;
+    float *fractions; // n x 2: closest safe, closest unsafe
 };
 
 __device__ __forceinline__ Sh qs_shape(const QsArgs &a, uint32_t type, float4 p) {
@@ -58,6 +69,7 @@ __device__ inline void qs_candidate(const QsArgs &a, uint32_t j, const Sh &qs, c
     if (cc >= (int)a.max_results) return;
     uint4 m = a.meta[j];
     if (m.w != a.space || !(m.y & a.mask)) return;
+    if (a.ex.n && q_excluded(a.ex, j)) return;
     BodyXf bx = a.xf[j];
     X3 xb(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
     if (!((m.x >> 8) & BF_SHAPE_IDENT)) {
@@ -66,9 +78,214 @@ __device__ inline void qs_candidate(const QsArgs &a, uint32_t j, const Sh &qs, c
     }
     Sh sb = qs_shape(a, m.x >> 24, a.shape_p[j]);
     Manifold *none = nullptr;
-    if (!solve_static<true>(qs, qx, sb, xb, *none, nullptr)) return;
+    // (ShapeParameters::margin grows the query shape: the withMargin routines, bradot_space_3d.cpp:241)
+    bool hit = a.margin != 0.f ? solve_static<true, true>(qs, qx, sb, xb, *none, nullptr, nullptr, nullptr, a.margin, 0.f)
+                               : solve_static<true>(qs, qx, sb, xb, *none, nullptr);
+    if (!hit) return;
     a.bodies[(size_t)r * a.max_results + cc] = (int32_t)j;
     cc++;
+}
+
+
+// Every leaf of the tree (and every unbounded static of the space) whose stored box meets [qmin, qmax]: f(body index).
+template <typename F>
+__device__ inline void qs_for_candidates(const QsArgs &a, V3 qmin, V3 qmax, F f) {
+    for (uint32_t k = a.big_start[a.space], ke = a.big_start[a.space + 1]; k < ke; k++) f(a.big[k]);
+    if (a.n_tree == 1) {
+        f(__float_as_uint(a.leaf_min[0].w));
+    } else if (a.n_tree > 1) {
+        uint32_t stack[128]; // as deep as the traversal of the step: key length plus the index tie-break
+        int sp = 0;
+        uint32_t node = 0;
+        while (true) {
+            const float4 *nd = a.nodes + (size_t)node * 4;
+            float4 lmin = nd[0], lmax = nd[1], rmin = nd[2], rmax = nd[3];
+            uint32_t child[2] = { __float_as_uint(lmin.w), __float_as_uint(rmin.w) };
+            uint32_t srange[2] = { __float_as_uint(lmax.w), __float_as_uint(rmax.w) };
+            bool hit[2];
+            hit[0] = a.space >= (srange[0] & 0xffffu) && a.space <= (srange[0] >> 16) &&
+                     !(lmin.x > qmax.x || lmin.y > qmax.y || lmin.z > qmax.z || qmin.x > lmax.x || qmin.y > lmax.y || qmin.z > lmax.z);
+            hit[1] = a.space >= (srange[1] & 0xffffu) && a.space <= (srange[1] >> 16) &&
+                     !(rmin.x > qmax.x || rmin.y > qmax.y || rmin.z > qmax.z || qmin.x > rmax.x || qmin.y > rmax.y || qmin.z > rmax.z);
+            for (int side = 0; side < 2; side++) {
+                if (hit[side] && (child[side] & QS_LEAF_BIT)) f(__float_as_uint(a.leaf_min[child[side] & ~QS_LEAF_BIT].w));
+            }
+            bool il = hit[0] && !(child[0] & QS_LEAF_BIT), ir = hit[1] && !(child[1] & QS_LEAF_BIT);
+            if (il) {
+                if (ir && sp < 128) stack[sp++] = child[1];
+                node = child[0];
+            } else if (ir) {
+                node = child[1];
+            } else {
+                if (sp == 0) break;
+                node = stack[--sp];
+            }
+        }
+    }
+}
+
+// the query shape of request r, its transform and its world box grown by `grow`
+__device__ inline void qs_request(const QsArgs &a, uint32_t r, float grow, Sh &qs, X3 &qx, V3 &qmin, V3 &qmax) {
+    const ShapeRec sr = a.shapes[a.shape_ids[r]];
+    float4 p = sr.p;
+    if (sr.meta.x == SH_CONVEX) p.x = __uint_as_float(sr.meta.y);
+    qs = qs_shape(a, sr.meta.x, p);
+    const float *f = a.xforms + (size_t)r * 12;
+    qx = X3(M3(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8])), V3(f[9], f[10], f[11]));
+    Box3 la;
+    la.pos = f4v(sr.aabb_pos);
+    la.size = f4v(sr.aabb_size);
+    Box3 box = xform_aabb(qx, la);
+    qmin = box.pos - V3(grow, grow, grow);
+    qmax = box.pos + box.size + V3(grow, grow, grow);
+}
+
+// world transform of body j's shape and the shape itself; false when the body is filtered out (space, mask, exclude list)
+__device__ inline bool qs_body(const QsArgs &a, uint32_t j, Sh &sb, X3 &xb) {
+    uint4 m = a.meta[j];
+    if (m.w != a.space || !(m.y & a.mask)) return false;
+    if (a.ex.n && q_excluded(a.ex, j)) return false;
+    BodyXf bx = a.xf[j];
+    xb = X3(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
+    if (!((m.x >> 8) & BF_SHAPE_IDENT)) {
+        BodyXf sx = a.shape_xf[j];
+        xb = xb * X3(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+    }
+    sb = qs_shape(a, m.x >> 24, a.shape_p[j]);
+    return true;
+}
+
+// the velocity of body j's surface at a world point (bradot_space_3d.cpp:368-372, 560-563)
+__device__ inline V3 qs_velocity_at(const QsArgs &a, uint32_t j, V3 point) {
+    if ((a.meta[j].x & 0xffu) == MODE_STATIC) return V3();
+    BodyVel v = a.vel[j];
+    BodyMassW mw = a.massw[j];
+    V3 rel = point - (f4v(a.xf[j].o) + V3(mw.i0.w, mw.i1.w, mw.i2.w));
+    return f4v(v.lin) + cross(f4v(v.ang), rel);
+}
+
+// rest_info (bradot_space_3d.cpp:513-569): the deepest contact of the query shape, grown by the margin, with anything it
+// touches -- the withMargin collision routines, the reference's rest callback.
+#define TEST_MOTION_MARGIN_MIN_VALUE 0.0001f
+#define TEST_MOTION_MIN_CONTACT_DEPTH_FACTOR 0.05f
+__global__ void __launch_bounds__(QS_THREADS) k_rest_info(QsArgs a) {
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= a.n) return;
+    float margin = fmaxf(a.margin, TEST_MOTION_MARGIN_MIN_VALUE);
+    Sh qs;
+    X3 qx;
+    V3 qmin, qmax;
+    qs_request(a, r, margin + 1e-4f, qs, qx, qmin, qmax);
+    RestSink sink;
+    V3 motion = a.motions ? V3(a.motions[r * 3], a.motions[r * 3 + 1], a.motions[r * 3 + 2]) : V3();
+    sink.min_allowed_depth = fminf(length(motion), margin * TEST_MOTION_MIN_CONTACT_DEPTH_FACTOR);
+    sink.best_len = 0.f;
+    sink.best_body = 0xffffffffu;
+    sink.contact = sink.normal = V3();
+    qs_for_candidates(a, qmin, qmax, [&](uint32_t j) {
+        Sh sb;
+        X3 xb;
+        if (!qs_body(a, j, sb, xb)) return;
+        sink.cur_body = j;
+        Manifold *none = nullptr;
+        solve_static<false, true>(qs, qx, sb, xb, *none, nullptr, nullptr, &sink, margin, 0.f);
+    });
+    bpc_rest_info o;
+    memset(&o, 0, sizeof(o));
+    o.body = -1;
+    if (sink.best_len != 0.f && sink.best_body != 0xffffffffu) {
+        o.hit = 1;
+        o.body = (int32_t)sink.best_body;
+        o.point[0] = sink.contact.x; o.point[1] = sink.contact.y; o.point[2] = sink.contact.z;
+        o.normal[0] = sink.normal.x; o.normal[1] = sink.normal.y; o.normal[2] = sink.normal.z;
+        V3 v = qs_velocity_at(a, sink.best_body, sink.contact);
+        o.linear_velocity[0] = v.x; o.linear_velocity[1] = v.y; o.linear_velocity[2] = v.z;
+    }
+    a.rest_out[r] = o;
+}
+
+// cast_motion (bradot_space_3d.cpp:264-381): how far the query shape can travel along `motion` before it touches anything --
+// per candidate a GJK distance test of the swept shape, then eight bisection steps on the travelled fraction.
+__global__ void __launch_bounds__(QS_THREADS) k_cast_motion(QsArgs a) {
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= a.n) return;
+    Sh qs;
+    X3 qx;
+    V3 qmin, qmax;
+    qs_request(a, r, 0.f, qs, qx, qmin, qmax);
+    const V3 motion(a.motions[r * 3], a.motions[r * 3 + 1], a.motions[r * 3 + 2]);
+    { // the box of the whole sweep, grown by the margin (:268-270)
+        V3 lo = qmin + motion, hi = qmax + motion;
+        float g = a.margin + 1e-4f;
+        qmin = V3(fminf(qmin.x, lo.x) - g, fminf(qmin.y, lo.y) - g, fminf(qmin.z, lo.z) - g);
+        qmax = V3(fmaxf(qmax.x, hi.x) + g, fmaxf(qmax.y, hi.y) + g, fmaxf(qmax.z, hi.z) + g);
+    }
+    const X3 xform_inv = affine_inverse(qx);
+    float best_safe = 1, best_unsafe = 1;
+    bool best_first = true;
+    V3 closest_A, closest_B;
+    uint32_t best_body = 0xffffffffu;
+    GjkBody A;
+    A.s = qs;
+    A.x = qx;
+    qs_for_candidates(a, qmin, qmax, [&](uint32_t j) {
+        GjkBody B;
+        if (!qs_body(a, j, B.s, B.x)) return;
+        B.motion = V3();
+        B.swept = false;
+        V3 point_A, point_B;
+        // does it collide if going all the way?
+        A.swept = true;
+        A.motion = xform(xform_inv.b, motion);
+        if (solve_distance(A, B, point_A, point_B)) return;
+        // objects it starts inside of are ignored
+        A.swept = false;
+        if (!solve_distance(A, B, point_A, point_B)) return;
+        A.swept = true;
+        float low = 0.0f, hi = 1.0f, fraction_coeff = 0.5f;
+        for (int k = 0; k < 8; k++) {
+            float fraction = low + (hi - low) * fraction_coeff;
+            A.motion = xform(xform_inv.b, motion * fraction);
+            V3 lA, lB;
+            bool collided = !solve_distance(A, B, lA, lB);
+            if (collided) {
+                hi = fraction;
+                // first time or alternating: bisect; colliding again: converge faster towards the low end
+                fraction_coeff = ((k == 0) || (low > 0.0f)) ? 0.5f : 0.25f;
+            } else {
+                point_A = lA;
+                point_B = lB;
+                low = fraction;
+                fraction_coeff = ((k == 0) || (hi < 1.0f)) ? 0.5f : 0.75f;
+            }
+        }
+        if (low < best_safe) {
+            best_first = true;
+            best_safe = low;
+            best_unsafe = hi;
+        }
+        if (best_first || (distance_squared(point_A, point_B) < distance_squared(closest_A, closest_B) && low <= best_safe)) {
+            closest_A = point_A;
+            closest_B = point_B;
+            best_body = j;
+            best_first = false;
+        }
+    });
+    a.fractions[r * 2] = best_safe;
+    a.fractions[r * 2 + 1] = best_unsafe;
+    bpc_rest_info o;
+    memset(&o, 0, sizeof(o));
+    o.body = -1;
+    if (best_body != 0xffffffffu) {
+        o.hit = 1;
+        o.body = (int32_t)best_body;
+        V3 nrm = normalized(closest_A - closest_B);
+        o.point[0] = closest_B.x; o.point[1] = closest_B.y; o.point[2] = closest_B.z;
+        o.normal[0] = nrm.x; o.normal[1] = nrm.y; o.normal[2] = nrm.z;
+        V3 v = qs_velocity_at(a, best_body, closest_B);
+        o.linear_velocity[0] = v.x; o.linear_velocity[1] = v.y; o.linear_velocity[2] = v.z;
+    }
+    a.rest_out[r] = o;
 }
 
 __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
@@ -84,7 +301,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
     la.pos = f4v(sr.aabb_pos);
     la.size = f4v(sr.aabb_size);
     Box3 box = xform_aabb(qx, la);
-    const float grow = 1e-4f; // the box test only nominates candidates
+    const float grow = 1e-4f + a.margin; // the box test only nominates candidates
     V3 qmin = box.pos - V3(grow, grow, grow), qmax = box.pos + box.size + V3(grow, grow, grow);
     int cc = 0;
     for (uint32_t k = a.big_start[a.space], ke = a.big_start[a.space + 1]; k < ke; k++) qs_candidate(a, a.big[k], qs, qx, r, cc);
@@ -133,6 +350,7 @@ struct QcArgs {
 __device__ inline void qc_candidate(const QsArgs &a, uint32_t j, const Sh &qs, const X3 &qx, RawSink &sink) {
     uint4 m = a.meta[j];
     if (m.w != a.space || !(m.y & a.mask)) return;
+    if (a.ex.n && q_excluded(a.ex, j)) return;
     BodyXf bx = a.xf[j];
     X3 xb(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
     if (!((m.x >> 8) & BF_SHAPE_IDENT)) {
@@ -141,7 +359,8 @@ __device__ inline void qc_candidate(const QsArgs &a, uint32_t j, const Sh &qs, c
     }
     Sh sb = qs_shape(a, m.x >> 24, a.shape_p[j]);
     Manifold *none = nullptr;
-    solve_static<false>(qs, qx, sb, xb, *none, nullptr, &sink);
+    if (a.margin != 0.f) solve_static<false, true>(qs, qx, sb, xb, *none, nullptr, &sink, nullptr, a.margin, 0.f); // (:419)
+    else solve_static<false>(qs, qx, sb, xb, *none, nullptr, &sink);
 }
 
 __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
@@ -158,7 +377,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
     la.pos = f4v(sr.aabb_pos);
     la.size = f4v(sr.aabb_size);
     Box3 box = xform_aabb(qx, la);
-    const float grow = 1e-4f;
+    const float grow = 1e-4f + a.margin;
     V3 qmin = box.pos - V3(grow, grow, grow), qmax = box.pos + box.size + V3(grow, grow, grow);
     V3 pts[QS_MAX_PAIRS * 2];
     RawSink sink;
@@ -206,7 +425,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
 }
 
 extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
-                                          int max_results, int32_t *out_counts, int32_t *out_bodies) {
+                                          float margin, int max_results, int32_t *out_counts, int32_t *out_bodies) {
     if (!ctx) return -1;
     if (space < 0 || (size_t)space >= ctx->spaces.size()) {
         ctx->err = "bpc_space_intersect_shapes: no such space";
@@ -239,6 +458,8 @@ extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, co
     a.space = (uint32_t)space;
     a.mask = collision_mask;
     a.max_results = (uint32_t)max_results;
+    a.margin = margin;
+    a.motions = nullptr;
     int32_t *d_ids = (int32_t *)ctx->staging.p;
     float *d_xf = ctx->staging.p + id_words;
     a.shape_ids = d_ids;
@@ -260,6 +481,8 @@ extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, co
     a.mindex = ctx->mindex.p;
     a.big = ctx->big_items.p;
     a.big_start = ctx->big_start.p;
+    a.ex.ids = ctx->q_exclude.p;
+    a.ex.n = ctx->n_q_exclude;
     BPC_CHECK(cudaMemcpyAsync(d_ids, shapes, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     BPC_CHECK(cudaMemcpyAsync(d_xf, xforms, xf_words * sizeof(float), cudaMemcpyHostToDevice, st));
     BPC_CHECK(cudaMemsetAsync(a.bodies, 0xff, body_words * sizeof(int32_t), st));
@@ -272,7 +495,7 @@ extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, co
 }
 
 extern "C" int bpc_space_collide_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
-                                        int max_results, int32_t *out_counts, float *out_points) {
+                                        float margin, int max_results, int32_t *out_counts, float *out_points) {
     if (!ctx) return -1;
     if (space < 0 || (size_t)space >= ctx->spaces.size()) {
         ctx->err = "bpc_space_collide_shapes: no such space";
@@ -306,6 +529,8 @@ extern "C" int bpc_space_collide_shapes(bpc_context *ctx, int space, int n, cons
     a.space = (uint32_t)space;
     a.mask = collision_mask;
     a.max_results = (uint32_t)max_results;
+    a.margin = margin;
+    a.motions = nullptr;
     int32_t *d_ids = (int32_t *)ctx->staging.p;
     float *d_xf = ctx->staging.p + id_words;
     a.shape_ids = d_ids;
@@ -328,6 +553,8 @@ extern "C" int bpc_space_collide_shapes(bpc_context *ctx, int space, int n, cons
     a.mindex = ctx->mindex.p;
     a.big = ctx->big_items.p;
     a.big_start = ctx->big_start.p;
+    a.ex.ids = ctx->q_exclude.p;
+    a.ex.n = ctx->n_q_exclude;
     BPC_CHECK(cudaMemcpyAsync(d_ids, shapes, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     BPC_CHECK(cudaMemcpyAsync(d_xf, xforms, xf_words * sizeof(float), cudaMemcpyHostToDevice, st));
     BPC_CHECK(cudaMemsetAsync(c.points, 0, pt_words * sizeof(float), st));
@@ -335,6 +562,130 @@ extern "C" int bpc_space_collide_shapes(bpc_context *ctx, int space, int n, cons
     BPC_CHECK(cudaGetLastError());
     BPC_CHECK(cudaMemcpyAsync(out_counts, a.counts, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     BPC_CHECK(cudaMemcpyAsync(out_points, c.points, pt_words * sizeof(float), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+
+// ---- rest_info / cast_motion: shared host side
+static int qs_check(bpc_context *ctx, const char *fn, int space, int n, const int32_t *shapes, const float *xforms) {
+    static thread_local std::string msg;
+    if (space < 0 || (size_t)space >= ctx->spaces.size()) {
+        msg = std::string(fn) + ": no such space";
+        ctx->err = msg.c_str();
+        return -1;
+    }
+    if (n < 0 || (n > 0 && (!shapes || !xforms))) {
+        msg = std::string(fn) + ": bad arguments";
+        ctx->err = msg.c_str();
+        return -1;
+    }
+    for (int i = 0; i < n; i++) {
+        if (shapes[i] < 0 || (size_t)shapes[i] >= ctx->h_shapes.size() || ctx->h_shapes[shapes[i]].meta.x == SH_PLANE) {
+            msg = std::string(fn) + ": invalid query shape (world boundaries cannot be query shapes)";
+            ctx->err = msg.c_str();
+            return -1;
+        }
+    }
+    return 0;
+}
+
+static void qs_fill(bpc_context *ctx, QsArgs &a, int space, int n, unsigned mask) {
+    memset(&a, 0, sizeof(a));
+    a.n = (uint32_t)n;
+    a.n_tree = ctx->n_tree;
+    a.space = (uint32_t)space;
+    a.mask = mask;
+    a.max_results = 1;
+    a.shapes = ctx->shapes.p;
+    a.nodes = ctx->nodes.p;
+    a.leaf_min = ctx->leaf_min.p;
+    a.meta = ctx->meta.p;
+    a.xf = ctx->xf.p;
+    a.shape_xf = ctx->shape_xf.p;
+    a.shape_p = ctx->shape_p.p;
+    a.meshes = ctx->meshes.p;
+    a.mverts = ctx->mverts.p;
+    a.mplanes = ctx->mplanes.p;
+    a.medges = ctx->medges.p;
+    a.mfaces = ctx->mfaces.p;
+    a.mindex = ctx->mindex.p;
+    a.big = ctx->big_items.p;
+    a.big_start = ctx->big_start.p;
+    a.ex.ids = ctx->q_exclude.p;
+    a.ex.n = ctx->n_q_exclude;
+    a.vel = ctx->vel.p;
+    a.massw = ctx->massw.p;
+}
+
+// staging layout: ids | xforms | motions | rest records | fractions
+static int qs_stage(bpc_context *ctx, QsArgs &a, int n, const int32_t *shapes, const float *xforms, const float *motions) {
+    cudaStream_t st = ctx->stream;
+    size_t id_words = ((size_t)n + 3) & ~(size_t)3, xf_words = (size_t)n * 12, mo_words = ((size_t)n * 3 + 3) & ~(size_t)3;
+    size_t rest_words = (size_t)n * (sizeof(bpc_rest_info) / 4), fr_words = (size_t)n * 2;
+    ctx->staging.reserve(id_words + xf_words + mo_words + rest_words + fr_words + 16, false, st);
+    if (!ctx->staging.p) {
+        ctx->err = "space query: out of device memory";
+        return -1;
+    }
+    float *base = ctx->staging.p;
+    a.shape_ids = (int32_t *)base;
+    a.xforms = base + id_words;
+    float *d_mo = base + id_words + xf_words;
+    a.motions = motions ? d_mo : nullptr;
+    a.rest_out = (bpc_rest_info *)(base + id_words + xf_words + mo_words);
+    a.fractions = base + id_words + xf_words + mo_words + rest_words;
+    BPC_CHECK(cudaMemcpyAsync((void *)a.shape_ids, shapes, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    BPC_CHECK(cudaMemcpyAsync((void *)a.xforms, xforms, xf_words * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (motions) BPC_CHECK(cudaMemcpyAsync(d_mo, motions, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+    return 0;
+}
+
+extern "C" int bpc_space_rest_infos(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, const float *motions,
+                                    float margin, unsigned collision_mask, bpc_rest_info *out) {
+    if (!ctx) return -1;
+    if (qs_check(ctx, "bpc_space_rest_infos", space, n, shapes, xforms)) return -1;
+    if (n > 0 && !out) {
+        ctx->err = "bpc_space_rest_infos: bad arguments";
+        return -1;
+    }
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (bpc_flush_tables(ctx)) return -1;
+    if (bpc_build_tree(ctx)) return -1;
+    QsArgs a;
+    qs_fill(ctx, a, space, n, collision_mask);
+    if (qs_stage(ctx, a, n, shapes, xforms, motions)) return -1;
+    a.margin = margin;
+    k_rest_info<<<(n + QS_THREADS - 1) / QS_THREADS, QS_THREADS, 0, st>>>(a);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaMemcpyAsync(out, a.rest_out, (size_t)n * sizeof(bpc_rest_info), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int bpc_space_cast_motions(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, const float *motions,
+                                      float margin, unsigned collision_mask, float *out_fractions, bpc_rest_info *out_info) {
+    if (!ctx) return -1;
+    if (qs_check(ctx, "bpc_space_cast_motions", space, n, shapes, xforms)) return -1;
+    if (n > 0 && (!motions || !out_fractions)) {
+        ctx->err = "bpc_space_cast_motions: bad arguments";
+        return -1;
+    }
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (bpc_flush_tables(ctx)) return -1;
+    if (bpc_build_tree(ctx)) return -1;
+    QsArgs a;
+    qs_fill(ctx, a, space, n, collision_mask);
+    if (qs_stage(ctx, a, n, shapes, xforms, motions)) return -1;
+    a.margin = margin;
+    k_cast_motion<<<(n + QS_THREADS - 1) / QS_THREADS, QS_THREADS, 0, st>>>(a);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaMemcpyAsync(out_fractions, a.fractions, (size_t)n * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (out_info) BPC_CHECK(cudaMemcpyAsync(out_info, a.rest_out, (size_t)n * sizeof(bpc_rest_info), cudaMemcpyDeviceToHost, st));
     BPC_CHECK(cudaStreamSynchronize(st));
     return 0;
 }

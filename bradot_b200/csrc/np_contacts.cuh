@@ -134,14 +134,41 @@ __device__ inline void raw_add(RawSink &r, V3 pA, V3 pB) {
     }
 }
 
+// Where a query (rest_info) wants the deepest contact only: _rest_cbk_result with no list of other results
+// (bradot_space_3d.cpp:453-511) -- contacts shallower than min_allowed_depth are ignored, the longest A->B distance wins.
+struct RestSink {
+    float min_allowed_depth;
+    float best_len;
+    V3 contact, normal;
+    uint32_t best_body, cur_body;
+};
+__device__ inline void rest_add(RestSink &r, V3 pA, V3 pB, V3 normal) {
+    float len = length(pB - pA);
+    if (len < r.min_allowed_depth) return;
+    if (!(len > r.best_len)) return;
+    r.best_len = len;
+    r.contact = pB;
+    r.normal = normal;
+    r.best_body = r.cur_body;
+}
+
 struct Collector {
     Manifold *m;
     RawSink *raw = nullptr;
+    RestSink *rest = nullptr;
     bool swap;
     bool collided;
     V3 normal;
     V3 *prev_axis;
-    __device__ __forceinline__ void call(V3 pA, V3 pB) {
+    float margin_A = 0.f, margin_B = 0.f; // the withMargin variants only (queries)
+    // _CollectorCallback::call (...sat.cpp:78-87): the normal is turned to point from A to B, then everything is swapped back
+    __device__ __forceinline__ void call(V3 pA, V3 pB, V3 nrm) {
+        if (rest) {
+            if (dot(nrm, pB - pA) < 0) nrm = -nrm;
+            if (swap) rest_add(*rest, pB, pA, -nrm);
+            else rest_add(*rest, pA, pB, nrm);
+            return;
+        }
         if (swap) {
             V3 t = pA;
             pA = pB;
@@ -150,6 +177,7 @@ struct Collector {
         if (raw) raw_add(*raw, pA, pB);
         else manifold_add(*m, pA, pB);
     }
+    __device__ __forceinline__ void call(V3 pA, V3 pB) { call(pA, pB, normal); }
 };
 
 __device__ inline void gen_point_point(const V3 *A, const V3 *B, Collector &c) { c.call(A[0], B[0]); }
@@ -158,7 +186,7 @@ __device__ inline void gen_point_edge(const V3 *A, const V3 *B, Collector &c) {
 }
 __device__ inline void gen_point_face(const V3 *A, const V3 *B, Collector &c) {
     Pl plane = pl_from_points(B[0], B[1], B[2]);
-    c.call(A[0], pl_project(plane, A[0]));
+    c.call(A[0], pl_project(plane, A[0]), plane.n); // the face's own normal, not the separating axis (...sat.cpp:121)
 }
 __device__ inline void sort4(float *d) {
 #define CSWAP(a, b) if (d[b] < d[a]) { float t = d[a]; d[a] = d[b]; d[b] = t; }
@@ -184,6 +212,14 @@ __device__ inline void gen_edge_edge(const V3 *A, const V3 *B, Collector &cb) {
     else if (d > 1.0f) d = 1.0f;
     V3 closest_A = A[0] + rel_A * d;
     V3 closest_B = closest_point_to_segment_uncapped(closest_A, B[0], B[1]);
+    if (cb.rest) { // only a sink that keeps the normal looks at it: perpendicular to both edges (...sat.cpp:177-185)
+        V3 normal = cross(rel_A, rel_B);
+        float normal_len = length(normal);
+        if (normal_len > 1e-3f) normal /= normal_len;
+        else normal = cb.normal;
+        cb.call(closest_A, closest_B, normal);
+        return;
+    }
     cb.call(closest_A, closest_B);
 }
 
@@ -226,7 +262,7 @@ __device__ inline void gen_face_face(const V3 *A, int nA, const V3 *B, int nB, C
         float d = pl_distance(plane_B, src[i]);
         V3 closest_B = src[i] - plane_B.n * d;
         if (dot(cb.normal, src[i]) >= dot(cb.normal, closest_B)) continue;
-        cb.call(src[i], closest_B);
+        cb.call(src[i], closest_B, plane_B.n); // the face's own normal (...sat.cpp:367)
     }
 }
 

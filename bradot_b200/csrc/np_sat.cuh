@@ -10,7 +10,10 @@
 #pragma once
 #include "np_contacts.cuh"
 
-struct Separator {
+// MG = the reference's withMargin variants (queries with a margin: rest_info, body_test_motion): both shapes are grown by
+// cb->margin_A / margin_B along every tested axis and the support points are pushed out by them.
+template <bool MG>
+struct SeparatorT {
     const Sh *A, *B;
     const X3 *xA, *xB;
     float best_depth;
@@ -27,6 +30,12 @@ struct Separator {
         float min_A = 0.f, max_A = 0.f, min_B = 0.f, max_B = 0.f;
         project_range(*A, axis, *xA, min_A, max_A);
         project_range(*B, axis, *xB, min_B, max_B);
+        if (MG) {
+            min_A -= cb->margin_A;
+            max_A += cb->margin_A;
+            min_B -= cb->margin_B;
+            max_B += cb->margin_B;
+        }
         min_B -= (max_A - min_A) * 0.5f;
         max_B += (max_A - min_A) * 0.5f;
         min_B -= (min_A + max_A) * 0.5f;
@@ -64,17 +73,28 @@ struct Separator {
         int nA, nB, tA, tB;
         get_supports(*A, normalized(xform_inv(xA->b, -best_axis)), sA, nA, tA);
         for (int i = 0; i < nA; i++) sA[i] = xform(*xA, sA[i]);
+        if (MG) {
+            for (int i = 0; i < nA; i++) sA[i] += -best_axis * cb->margin_A;
+        }
         get_supports(*B, normalized(xform_inv(xB->b, best_axis)), sB, nB, tB);
         for (int i = 0; i < nB; i++) sB[i] = xform(*xB, sB[i]);
+        if (MG) {
+            for (int i = 0; i < nB; i++) sB[i] += best_axis * cb->margin_B;
+        }
         cb->normal = best_axis;
         if (cb->prev_axis) *cb->prev_axis = best_axis;
         if (nA >= 1 && nB >= 1) generate_contacts_from_supports(sA, nA, tA, sB, nB, tB, *cb);
         cb->collided = true;
     }
 };
+typedef SeparatorT<false> Separator;
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void analytic_sphere_collision(V3 oa, float ra, V3 ob, float rb, Collector &c) {
+    if (MG) {
+        ra += c.margin_A;
+        rb += c.margin_B;
+    }
     V3 b_to_a = oa - ob;
     float len = length(b_to_a);
     float overlap = ra + rb - len;
@@ -86,20 +106,20 @@ __device__ inline void analytic_sphere_collision(V3 oa, float ra, V3 ob, float r
     if (ra < rb) {
         V3 pa = oa - b_to_a * ra;
         V3 pb = pa + b_to_a * overlap;
-        c.call(pa, pb);
+        c.call(pa, pb, b_to_a);
     } else {
         V3 pb = ob + b_to_a * rb;
         V3 pa = pb - b_to_a * overlap;
-        c.call(pa, pb);
+        c.call(pa, pb, b_to_a);
     }
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_sphere_sphere(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
-    analytic_sphere_collision<TEST>(xa.o, a.p.x * length(xa.b.r[0]), xb.o, b.p.x * length(xb.b.r[0]), c);
+    analytic_sphere_collision<TEST, MG>(xa.o, a.p.x * length(xa.b.r[0]), xb.o, b.p.x * length(xb.b.r[0]), c);
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_sphere_box(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     V3 center = xform(affine_inverse(xb), xa.o);
     V3 ext(b.p.x, b.p.y, b.p.z);
@@ -108,24 +128,26 @@ __device__ inline void col_sphere_box(const Sh &a, const X3 &xa, const Sh &b, co
     V3 delta = nearest - xa.o;
     float len = length(delta);
     float radius = a.p.x * length(xa.b.r[0]);
-    if (len > radius + 0.f + 0.f) return;
+    const float mA = MG ? c.margin_A : 0.f, mB = MG ? c.margin_B : 0.f;
+    if (len > radius + mA + mB) return;
     c.collided = true;
     if (TEST) return;
     V3 axis;
     if (len == 0) axis = normalized(xb.o - nearest);
     else axis = delta / len;
-    V3 pa = xa.o + (radius + 0.f) * axis;
-    c.call(pa, nearest);
+    V3 pa = xa.o + (radius + mA) * axis;
+    V3 pb = MG ? nearest - mB * axis : nearest;
+    c.call(pa, pb, axis);
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_sphere_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     float scale_A = length(xa.b.r[0]);
     float scale_B = length(xb.b.r[0]);
     V3 cap_axis = xb.b.col(1) * (b.p.y * 0.5f - b.p.x);
     V3 s0 = xb.o + cap_axis, s1 = xb.o - cap_axis;
     V3 closest = closest_point_to_segment(xa.o, s0, s1);
-    analytic_sphere_collision<TEST>(xa.o, a.p.x * scale_A, closest, b.p.x * scale_B, c);
+    analytic_sphere_collision<TEST, MG>(xa.o, a.p.x * scale_A, closest, b.p.x * scale_B, c);
 }
 
 // geometry_3d.cpp:36-131 (David Eberly's segment-segment distance)
@@ -193,7 +215,7 @@ __device__ inline void closest_points_between_segments(V3 p0, V3 p1, V3 q0, V3 q
     qt = (1 - t) * q0 + t * q1;
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_capsule_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
     float scale_A = length(xa.b.r[0]);
     float scale_B = length(xb.b.r[0]);
@@ -201,16 +223,16 @@ __device__ inline void col_capsule_capsule(const Sh &a, const X3 &xa, const Sh &
     V3 axB = xb.b.col(1) * (b.p.y * 0.5f - b.p.x);
     V3 ca, cbp;
     closest_points_between_segments(xa.o + axA, xa.o - axA, xb.o + axB, xb.o - axB, ca, cbp);
-    analytic_sphere_collision<TEST>(ca, a.p.x * scale_A, cbp, b.p.x * scale_B, c);
+    analytic_sphere_collision<TEST, MG>(ca, a.p.x * scale_A, cbp, b.p.x * scale_B, c);
 }
 
 __device__ inline V3 box_corner_toward(const Sh &box, const X3 &xf, V3 cn) {
     return xform(xf, V3((cn.x < 0) ? -box.p.x : box.p.x, (cn.y < 0) ? -box.p.y : box.p.y, (cn.z < 0) ? -box.p.z : box.p.z));
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_box_box(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
-    Separator sep;
+    SeparatorT<MG> sep;
     sep.init(&a, &xa, &b, &xb, &c);
     if (!sep.test_previous_axis()) return;
     for (int i = 0; i < 3; i++) {
@@ -227,12 +249,25 @@ __device__ inline void col_box_box(const Sh &a, const X3 &xa, const Sh &b, const
             if (!sep.test_axis(axis)) return;
         }
     }
+    if (MG) { // ...sat.cpp:1122-1168: closest corners, then the edges as cylinders
+        V3 ab_vec = xb.o - xa.o;
+        V3 support_a = box_corner_toward(a, xa, xform_inv(xa.b, ab_vec));
+        V3 support_b = box_corner_toward(b, xb, xform_inv(xb.b, -ab_vec));
+        V3 axis_ab = support_a - support_b;
+        if (!sep.test_axis(normalized(axis_ab))) return;
+        for (int i = 0; i < 3; i++) {
+            V3 axis_a = xa.b.col(i);
+            if (!sep.test_axis(normalized(cross(cross(axis_ab, axis_a), axis_a)))) return;
+            V3 axis_b = xb.b.col(i);
+            if (!sep.test_axis(normalized(cross(cross(axis_ab, axis_b), axis_b)))) return;
+        }
+    }
     sep.template generate_contacts<TEST>();
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_box_capsule(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
-    Separator sep;
+    SeparatorT<MG> sep;
     sep.init(&a, &xa, &b, &xb, &c);
     if (!sep.test_previous_axis()) return;
     for (int i = 0; i < 3; i++) {
@@ -276,9 +311,9 @@ __device__ inline void col_box_capsule(const Sh &a, const X3 &xa, const Sh &b, c
     sep.template generate_contacts<TEST>();
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_sphere_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
-    Separator sep;
+    SeparatorT<MG> sep;
     sep.init(&a, &xa, &b, &xb, &c);
     if (!sep.test_previous_axis()) return;
     const MeshView &m = b.m;
@@ -299,9 +334,9 @@ __device__ inline void col_sphere_convex(const Sh &a, const X3 &xa, const Sh &b,
     sep.template generate_contacts<TEST>();
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_box_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
-    Separator sep;
+    SeparatorT<MG> sep;
     sep.init(&a, &xa, &b, &xb, &c);
     if (!sep.test_previous_axis()) return;
     const MeshView &m = b.m;
@@ -320,12 +355,43 @@ __device__ inline void col_box_convex(const Sh &a, const X3 &xa, const Sh &b, co
             if (!sep.test_axis(normalized(cross(e1, e2)))) return;
         }
     }
+    if (MG) { // ...sat.cpp:1440-1497: hull vertices against box corners / edges, box corners against hull edges
+        for (uint32_t v = 0; v < m.nv; v++) {
+            V3 vtxb = xform(xb, mv_vert(m, v));
+            V3 ab_vec = vtxb - xa.o;
+            V3 support_a = box_corner_toward(a, xa, xform_inv(xa.b, ab_vec));
+            V3 axis_ab = support_a - vtxb;
+            if (!sep.test_axis(normalized(axis_ab))) return;
+            for (int i = 0; i < 3; i++) {
+                V3 axis_a = xa.b.col(i);
+                if (!sep.test_axis(normalized(cross(cross(axis_ab, axis_a), axis_a)))) return;
+            }
+        }
+        for (int i = 0; i < 2; i++) {
+            for (int j = 0; j < 2; j++) {
+                for (int k = 0; k < 2; k++) {
+                    V3 he(a.p.x, a.p.y, a.p.z);
+                    he.x *= (i * 2 - 1);
+                    he.y *= (j * 2 - 1);
+                    he.z *= (k * 2 - 1);
+                    V3 point = xa.o;
+                    for (int l = 0; l < 3; l++) point += xa.b.col(l) * comp(he, l);
+                    for (uint32_t e = 0; e < m.ne; e++) {
+                        uint4 ed = __ldg(&m.edges[e]);
+                        V3 p1 = xform(xb, mv_vert(m, ed.x)), p2 = xform(xb, mv_vert(m, ed.y));
+                        V3 n = p2 - p1;
+                        if (!sep.test_axis(normalized(cross(cross(point - p2, n), n)))) return;
+                    }
+                }
+            }
+        }
+    }
     sep.template generate_contacts<TEST>();
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_capsule_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
-    Separator sep;
+    SeparatorT<MG> sep;
     sep.init(&a, &xa, &b, &xb, &c);
     if (!sep.test_previous_axis()) return;
     const MeshView &m = b.m;
@@ -356,9 +422,9 @@ __device__ __forceinline__ bool is_minkowski_face(V3 A, V3 B, V3 B_x_A, V3 C, V3
     return (CBA * DBA < 0.0f) && (ADC * BDC < 0.0f) && (CBA * BDC > 0.0f);
 }
 
-template <bool TEST>
+template <bool TEST, bool MG = false>
 __device__ inline void col_convex_convex(const Sh &a, const X3 &xa, const Sh &b, const X3 &xb, Collector &c) {
-    Separator sep;
+    SeparatorT<MG> sep;
     sep.init(&a, &xa, &b, &xb, &c);
     if (!sep.test_previous_axis()) return;
     const MeshView &ma = a.m, &mb = b.m;
@@ -387,12 +453,38 @@ __device__ inline void col_convex_convex(const Sh &a, const X3 &xa, const Sh &b,
             }
         }
     }
+    if (MG) { // ...sat.cpp:2121-2160: vertex-vertex, then edge-vertex both ways
+        for (uint32_t i = 0; i < ma.nv; i++) {
+            V3 va = xform(xa, mv_vert(ma, i));
+            for (uint32_t j = 0; j < mb.nv; j++) {
+                if (!sep.test_axis(normalized(va - xform(xb, mv_vert(mb, j))))) return;
+            }
+        }
+        for (uint32_t i = 0; i < ma.ne; i++) {
+            uint4 ea = __ldg(&ma.edges[i]);
+            V3 e1 = xform(xa.b, mv_vert(ma, ea.x)), e2 = xform(xa.b, mv_vert(ma, ea.y));
+            V3 n = e2 - e1;
+            for (uint32_t j = 0; j < mb.nv; j++) {
+                V3 e3 = xform(xb, mv_vert(mb, j));
+                if (!sep.test_axis(normalized(cross(cross(e1 - e3, n), n)))) return;
+            }
+        }
+        for (uint32_t i = 0; i < mb.ne; i++) {
+            uint4 eb = __ldg(&mb.edges[i]);
+            V3 e1 = xform(xb.b, mv_vert(mb, eb.x)), e2 = xform(xb.b, mv_vert(mb, eb.y));
+            V3 n = e2 - e1;
+            for (uint32_t j = 0; j < ma.nv; j++) {
+                V3 e3 = xform(xa, mv_vert(ma, j));
+                if (!sep.test_axis(normalized(cross(cross(e1 - e3, n), n)))) return;
+            }
+        }
+    }
     sep.template generate_contacts<TEST>();
 }
 
 // plane (world boundary, shape A of the call) against any supported shape
-template <bool TEST>
-__device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, const X3 &xb, Collector &c, bool swap_result) {
+template <bool TEST, bool MG = false>
+__device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, const X3 &xb, Collector &c, bool swap_result, float margin = 0.f) {
     // Transform3D::xform(Plane): transform_3d.h:154-158, 241-252
     M3 bit = transposed(inverse(xp.b));
     V3 pn(pl_shape.p.x, pl_shape.p.y, pl_shape.p.z);
@@ -405,23 +497,26 @@ __device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, 
     get_supports(b, normalized(xform_inv(xb.b, -p.n)), sup, n, type);
     bool found = false;
     for (int i = 0; i < n; i++) {
+        if (MG) sup[i] += margin * normalized(sup[i]); // (...collision_solver_3d.cpp:73: in the shape's own space, away from its origin)
         V3 s = xform(xb, sup[i]);
         if (pl_distance(p, s) >= 0) continue;
         found = true;
         if (TEST) return true;
         V3 sa = pl_project(p, s);
         c.swap = swap_result;
-        c.call(sa, s);
+        c.call(sa, s, normalized(s - sa));
     }
     return found;
 }
 
 // BradotCollisionSolver3D::solve_static (…collision_solver_3d.cpp:362-435) + sat_calculate_penetration dispatch (…sat.cpp:2296-2421)
-template <bool TEST>
-__device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, const X3 &xb, Manifold &m, V3 *sep_axis, RawSink *raw = nullptr) {
+template <bool TEST, bool MG = false>
+__device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, const X3 &xb, Manifold &m, V3 *sep_axis, RawSink *raw = nullptr,
+                                    RestSink *rest = nullptr, float margin_A = 0.f, float margin_B = 0.f) {
     Collector c;
     c.m = &m;
     c.raw = raw;
+    c.rest = rest;
     c.swap = false;
     c.collided = false;
     c.prev_axis = sep_axis;
@@ -429,8 +524,8 @@ __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, co
     uint32_t ta = sa.type, tb = sb.type;
     if (min(ta, tb) == SH_PLANE) {
         if (ta == SH_PLANE && tb == SH_PLANE) return false;
-        if (ta > tb) return col_plane<TEST>(sb, xb, sa, xa, c, true);
-        return col_plane<TEST>(sa, xa, sb, xb, c, false);
+        if (ta > tb) return col_plane<TEST, MG>(sb, xb, sa, xa, c, true, margin_A);
+        return col_plane<TEST, MG>(sa, xa, sb, xb, c, false, margin_B);
     }
     // ordered by shape type; swapped BY VALUE: pointers to whichever of two locals would pin all four in local memory
     const bool swap = ta > tb;
@@ -440,20 +535,24 @@ __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, co
         uint32_t t = ta; ta = tb; tb = t;
         c.swap = true;
     }
+    if (MG) {
+        c.margin_A = swap ? margin_B : margin_A;
+        c.margin_B = swap ? margin_A : margin_B;
+    }
     if (ta == SH_SPHERE) {
-        if (tb == SH_SPHERE) col_sphere_sphere<TEST>(A, XA, B, XB, c);
-        else if (tb == SH_BOX) col_sphere_box<TEST>(A, XA, B, XB, c);
-        else if (tb == SH_CAPSULE) col_sphere_capsule<TEST>(A, XA, B, XB, c);
-        else if (tb == SH_CONVEX) col_sphere_convex<TEST>(A, XA, B, XB, c);
+        if (tb == SH_SPHERE) col_sphere_sphere<TEST, MG>(A, XA, B, XB, c);
+        else if (tb == SH_BOX) col_sphere_box<TEST, MG>(A, XA, B, XB, c);
+        else if (tb == SH_CAPSULE) col_sphere_capsule<TEST, MG>(A, XA, B, XB, c);
+        else if (tb == SH_CONVEX) col_sphere_convex<TEST, MG>(A, XA, B, XB, c);
     } else if (ta == SH_BOX) {
-        if (tb == SH_BOX) col_box_box<TEST>(A, XA, B, XB, c);
-        else if (tb == SH_CAPSULE) col_box_capsule<TEST>(A, XA, B, XB, c);
-        else if (tb == SH_CONVEX) col_box_convex<TEST>(A, XA, B, XB, c);
+        if (tb == SH_BOX) col_box_box<TEST, MG>(A, XA, B, XB, c);
+        else if (tb == SH_CAPSULE) col_box_capsule<TEST, MG>(A, XA, B, XB, c);
+        else if (tb == SH_CONVEX) col_box_convex<TEST, MG>(A, XA, B, XB, c);
     } else if (ta == SH_CAPSULE) {
-        if (tb == SH_CAPSULE) col_capsule_capsule<TEST>(A, XA, B, XB, c);
-        else if (tb == SH_CONVEX) col_capsule_convex<TEST>(A, XA, B, XB, c);
+        if (tb == SH_CAPSULE) col_capsule_capsule<TEST, MG>(A, XA, B, XB, c);
+        else if (tb == SH_CONVEX) col_capsule_convex<TEST, MG>(A, XA, B, XB, c);
     } else if (ta == SH_CONVEX && tb == SH_CONVEX) {
-        col_convex_convex<TEST>(A, XA, B, XB, c);
+        col_convex_convex<TEST, MG>(A, XA, B, XB, c);
     }
     return c.collided;
 }

@@ -45,6 +45,7 @@ EXPORTS = [
     "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_test_segment_math", "bpc_bodies_set_exception",
     "bpc_bodies_set_max_contacts_reported", "bpc_body_read_contacts", "bpc_contacts_capacity", "bpc_contacts_read",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
+    "bpc_space_set_query_exclude", "bpc_space_rest_infos", "bpc_space_cast_motions",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
 
@@ -61,6 +62,7 @@ class PhysicsError(RuntimeError):
 
 CONTACT_DT = np.dtype([("local_pos", "<f4", 3), ("depth", "<f4"), ("local_normal", "<f4", 3), ("collider", "<i4"), ("local_velocity", "<f4", 3),
                        ("collider_pos", "<f4", 3), ("collider_velocity", "<f4", 3), ("impulse", "<f4", 3)])
+REST_INFO_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("point", "<f4", 3), ("normal", "<f4", 3), ("linear_velocity", "<f4", 3)])
 RAY_RESULT_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("position", "<f4", 3), ("normal", "<f4", 3)])
 
 
@@ -108,8 +110,11 @@ def load_library(path=LIB_PATH):
     lib.bpc_step.argtypes = [vp, cf]
     lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
     lib.bpc_space_intersect_points.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp, vp]
-    lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, ci, vp, vp]
-    lib.bpc_space_collide_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, ci, vp, vp]
+    lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
+    lib.bpc_space_collide_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
+    lib.bpc_space_set_query_exclude.argtypes = [vp, vp, ci]
+    lib.bpc_space_rest_infos.argtypes = [vp, ci, ci, vp, vp, vp, cf, ctypes.c_uint, vp]
+    lib.bpc_space_cast_motions.argtypes = [vp, ci, ci, vp, vp, vp, cf, ctypes.c_uint, vp, vp]
     lib.bpc_synchronize.argtypes = [vp]
     lib.bpc_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
     lib.bpc_pair_count.argtypes = [vp]
@@ -370,7 +375,7 @@ class PhysicsServerCUDA:
                                                         _ptr(counts), _ptr(bodies)))
         return counts, bodies
 
-    def intersect_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=32):
+    def intersect_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=32, margin=0.0):
         """Batched PhysicsDirectSpaceState3D.intersect_shape: shape handles (n) placed at xforms (n, 12)."""
         sh = np.ascontiguousarray(shapes, np.int32).reshape(-1)
         xf = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
@@ -378,18 +383,44 @@ class PhysicsServerCUDA:
         counts = np.zeros(len(sh), np.int32)
         bodies = np.full((len(sh), max_results), -1, np.int32)
         self._check(self.lib.bpc_space_intersect_shapes(self.ctx, int(space), len(sh), _ptr(sh), _ptr(xf), ctypes.c_uint(collision_mask),
-                                                        int(max_results), _ptr(counts), _ptr(bodies)))
+                                                        ctypes.c_float(margin), int(max_results), _ptr(counts), _ptr(bodies)))
         return counts, bodies
 
-    def collide_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=16):
+    def collide_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=16, margin=0.0):
         """Batched PhysicsDirectSpaceState3D.collide_shape: (counts int32[n], points float32[n, max_results, 2, 3])."""
         sh = np.ascontiguousarray(shapes, np.int32).reshape(-1)
         xf = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
         counts = np.zeros(len(sh), np.int32)
         pts = np.zeros((len(sh), max_results, 2, 3), np.float32)
         self._check(self.lib.bpc_space_collide_shapes(self.ctx, int(space), len(sh), _ptr(sh), _ptr(xf), ctypes.c_uint(collision_mask),
-                                                      int(max_results), _ptr(counts), _ptr(pts)))
+                                                      ctypes.c_float(margin), int(max_results), _ptr(counts), _ptr(pts)))
         return counts, pts
+
+    def set_query_exclude(self, bodies):
+        """Bodies every following space query skips (the `exclude` list of the query parameters); empty clears."""
+        b = np.ascontiguousarray(bodies, np.int32).reshape(-1)
+        self._check(self.lib.bpc_space_set_query_exclude(self.ctx, _ptr(b) if len(b) else None, len(b)))
+
+    def rest_infos(self, shapes, xforms, motions=None, margin=0.0, space=0, collision_mask=0xFFFFFFFF):
+        """Batched PhysicsDirectSpaceState3D.rest_info: structured array REST_INFO_DT, one record per query."""
+        sh = np.ascontiguousarray(shapes, np.int32).reshape(-1)
+        xf = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
+        mo = None if motions is None else np.ascontiguousarray(motions, np.float32).reshape(-1, 3)
+        out = np.zeros(len(sh), REST_INFO_DT)
+        self._check(self.lib.bpc_space_rest_infos(self.ctx, int(space), len(sh), _ptr(sh), _ptr(xf), None if mo is None else _ptr(mo),
+                                                  ctypes.c_float(margin), ctypes.c_uint(collision_mask), _ptr(out)))
+        return out
+
+    def cast_motions(self, shapes, xforms, motions, margin=0.0, space=0, collision_mask=0xFFFFFFFF):
+        """Batched PhysicsDirectSpaceState3D.cast_motion: (fractions float32[n, 2] = closest safe / unsafe, REST_INFO_DT[n])."""
+        sh = np.ascontiguousarray(shapes, np.int32).reshape(-1)
+        xf = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
+        mo = np.ascontiguousarray(motions, np.float32).reshape(-1, 3)
+        fr = np.zeros((len(sh), 2), np.float32)
+        info = np.zeros(len(sh), REST_INFO_DT)
+        self._check(self.lib.bpc_space_cast_motions(self.ctx, int(space), len(sh), _ptr(sh), _ptr(xf), _ptr(mo), ctypes.c_float(margin),
+                                                    ctypes.c_uint(collision_mask), _ptr(fr), _ptr(info)))
+        return fr, info
 
     def set_solve_order(self, order):
         o = np.ascontiguousarray(order, np.int32).reshape(-1, 3)

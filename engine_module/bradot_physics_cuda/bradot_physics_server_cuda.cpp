@@ -155,6 +155,30 @@ PhysicsDirectSpaceState3D *BradotPhysicsServerCUDA::space_get_direct_state(RID p
 	return space->direct_state;
 }
 
+// The exclude list of a query (RayParameters / PointParameters / ShapeParameters ::exclude) for the duration of one call:
+// RIDs mapped to body slots, handed to the backend, cleared again on the way out.
+struct BpcExcludeScope {
+	bpc_context *ctx = nullptr;
+	bool set = false;
+	BpcExcludeScope(BradotPhysicsServerCUDA *p_server, bpc_context *p_ctx, const HashSet<RID> &p_exclude, LocalVector<int32_t> &r_slots) {
+		ctx = p_ctx;
+		for (const RID &r : p_exclude) {
+			int32_t slot = p_server->body_slot_of(r);
+			if (slot >= 0) {
+				r_slots.push_back(slot);
+			}
+		}
+		if (!r_slots.is_empty()) {
+			set = bpc_space_set_query_exclude(ctx, r_slots.ptr(), (int)r_slots.size()) == 0;
+		}
+	}
+	~BpcExcludeScope() {
+		if (set) {
+			bpc_space_set_query_exclude(ctx, nullptr, 0);
+		}
+	}
+};
+
 int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit) {
 	ERR_FAIL_NULL_V(server, 0);
 	ERR_FAIL_COND_V(p_from_to.size() % 2, 0);
@@ -193,11 +217,13 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 
 int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) {
 	ERR_FAIL_NULL_V(server, 0);
-	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas, 0, "BradotPhysicsCUDA: intersect_point with exclude lists or areas is not supported yet.");
+	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, 0, "BradotPhysicsCUDA: intersect_point with areas is not supported yet.");
 	if (p_result_max <= 0 || !p_parameters.collide_with_bodies) {
 		return 0;
 	}
 	server->_flush_pending();
+	LocalVector<int32_t> excluded;
+	BpcExcludeScope exclude_scope(server, server->ctx, p_parameters.exclude, excluded);
 	int max_r = p_result_max > 2048 ? 2048 : p_result_max;
 	float p[3] = { (float)p_parameters.position.x, (float)p_parameters.position.y, (float)p_parameters.position.z };
 	int32_t count = 0;
@@ -220,8 +246,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_
 
 int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) {
 	ERR_FAIL_NULL_V(server, 0);
-	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.margin != 0.0, 0,
-			"BradotPhysicsCUDA: intersect_shape with exclude lists, areas or a margin is not supported yet.");
+	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, 0, "BradotPhysicsCUDA: intersect_shape with areas is not supported yet.");
 	if (p_result_max <= 0 || !p_parameters.collide_with_bodies) {
 		return 0;
 	}
@@ -236,7 +261,9 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_
 	int32_t count = 0;
 	LocalVector<int32_t> slots;
 	slots.resize(max_r);
-	ERR_FAIL_COND_V_MSG(bpc_space_intersect_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	LocalVector<int32_t> excluded;
+	BpcExcludeScope exclude_scope(server, server->ctx, p_parameters.exclude, excluded);
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, p_parameters.margin, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
 	int cc = 0;
 	for (int i = 0; i < count; i++) {
 		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size() || !server->body_of_slot[slots[i]]) {
@@ -256,8 +283,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_
 bool BradotPhysicsDirectSpaceStateCUDA::collide_shape(const ShapeParameters &p_parameters, Vector3 *r_results, int p_result_max, int &r_result_count) {
 	r_result_count = 0;
 	ERR_FAIL_NULL_V(server, false);
-	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.margin != 0.0, false,
-			"BradotPhysicsCUDA: collide_shape with exclude lists, areas or a margin is not supported yet.");
+	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, false, "BradotPhysicsCUDA: collide_shape with areas is not supported yet.");
 	if (p_result_max <= 0 || !r_results || !p_parameters.collide_with_bodies) {
 		return false;
 	}
@@ -272,7 +298,9 @@ bool BradotPhysicsDirectSpaceStateCUDA::collide_shape(const ShapeParameters &p_p
 	int32_t count = 0;
 	LocalVector<float> pts;
 	pts.resize(max_r * 6);
-	ERR_FAIL_COND_V_MSG(bpc_space_collide_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, max_r, &count, pts.ptr()) < 0, false, bpc_last_error(server->ctx));
+	LocalVector<int32_t> excluded;
+	BpcExcludeScope exclude_scope(server, server->ctx, p_parameters.exclude, excluded);
+	ERR_FAIL_COND_V_MSG(bpc_space_collide_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, p_parameters.margin, max_r, &count, pts.ptr()) < 0, false, bpc_last_error(server->ctx));
 	for (int i = 0; i < count * 2; i++) {
 		r_results[i] = Vector3(pts[i * 3 + 0], pts[i * 3 + 1], pts[i * 3 + 2]);
 	}
@@ -280,12 +308,82 @@ bool BradotPhysicsDirectSpaceStateCUDA::collide_shape(const ShapeParameters &p_p
 	return count > 0;
 }
 
-bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_parameters, RayResult &r_result) {
-	ERR_FAIL_COND_V_MSG(!p_parameters.exclude.is_empty() || p_parameters.collide_with_areas || p_parameters.pick_ray, false,
-			"BradotPhysicsCUDA: intersect_ray with exclude lists, areas or pick_ray is not supported yet.");
+// what bpc_space_rest_infos / bpc_space_cast_motions report about a body, as the engine's ShapeRestInfo
+void BradotPhysicsDirectSpaceStateCUDA::_fill_rest_info(const bpc_rest_info &p_info, ShapeRestInfo *r_info) const {
+	BradotPhysicsServerCUDA::Body *b = (p_info.body >= 0 && (uint32_t)p_info.body < server->body_of_slot.size()) ? server->body_of_slot[p_info.body] : nullptr;
+	r_info->point = Vector3(p_info.point[0], p_info.point[1], p_info.point[2]);
+	r_info->normal = Vector3(p_info.normal[0], p_info.normal[1], p_info.normal[2]);
+	r_info->linear_velocity = Vector3(p_info.linear_velocity[0], p_info.linear_velocity[1], p_info.linear_velocity[2]);
+	r_info->rid = b ? b->self : RID();
+	r_info->collider_id = b ? b->instance_id : ObjectID();
+	r_info->shape = 0;
+}
+
+bool BradotPhysicsDirectSpaceStateCUDA::cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info) {
+	p_closest_safe = 1;
+	p_closest_unsafe = 1;
+	ERR_FAIL_NULL_V(server, false);
+	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, false, "BradotPhysicsCUDA: cast_motion with areas is not supported yet.");
+	if (!p_parameters.collide_with_bodies) {
+		return true;
+	}
+	BradotPhysicsServerCUDA::Shape *shape = server->shape_owner.get_or_null(p_parameters.shape_rid);
+	ERR_FAIL_NULL_V(shape, false);
+	int32_t handle = server->_shape_handle(shape);
+	ERR_FAIL_COND_V(handle < 0, false);
+	server->_flush_pending();
+	float f[12];
+	_xf_to_floats(p_parameters.transform, f);
+	float motion[3] = { (float)p_parameters.motion.x, (float)p_parameters.motion.y, (float)p_parameters.motion.z };
+	float fractions[2] = { 1.f, 1.f };
+	bpc_rest_info info;
+	LocalVector<int32_t> excluded;
+	BpcExcludeScope exclude_scope(server, server->ctx, p_parameters.exclude, excluded);
+	ERR_FAIL_COND_V_MSG(bpc_space_cast_motions(server->ctx, space_handle, 1, &handle, f, motion, p_parameters.margin, p_parameters.collision_mask, fractions, &info) < 0, false, bpc_last_error(server->ctx));
+	p_closest_safe = fractions[0];
+	p_closest_unsafe = fractions[1];
+	if (r_info && info.hit) {
+		_fill_rest_info(info, r_info);
+	}
+	return true;
+}
+
+bool BradotPhysicsDirectSpaceStateCUDA::rest_info(const ShapeParameters &p_parameters, ShapeRestInfo *r_info) {
+	ERR_FAIL_NULL_V(server, false);
+	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, false, "BradotPhysicsCUDA: rest_info with areas is not supported yet.");
 	if (!p_parameters.collide_with_bodies) {
 		return false;
 	}
+	BradotPhysicsServerCUDA::Shape *shape = server->shape_owner.get_or_null(p_parameters.shape_rid);
+	ERR_FAIL_NULL_V(shape, false);
+	int32_t handle = server->_shape_handle(shape);
+	ERR_FAIL_COND_V(handle < 0, false);
+	server->_flush_pending();
+	float f[12];
+	_xf_to_floats(p_parameters.transform, f);
+	float motion[3] = { (float)p_parameters.motion.x, (float)p_parameters.motion.y, (float)p_parameters.motion.z };
+	bpc_rest_info info;
+	LocalVector<int32_t> excluded;
+	BpcExcludeScope exclude_scope(server, server->ctx, p_parameters.exclude, excluded);
+	ERR_FAIL_COND_V_MSG(bpc_space_rest_infos(server->ctx, space_handle, 1, &handle, f, motion, p_parameters.margin, p_parameters.collision_mask, &info) < 0, false, bpc_last_error(server->ctx));
+	if (!info.hit) {
+		return false;
+	}
+	if (r_info) {
+		_fill_rest_info(info, r_info);
+	}
+	return true;
+}
+
+bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_parameters, RayResult &r_result) {
+	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas || p_parameters.pick_ray, false, "BradotPhysicsCUDA: intersect_ray with areas or pick_ray is not supported yet.");
+	if (!p_parameters.collide_with_bodies) {
+		return false;
+	}
+	ERR_FAIL_NULL_V(server, false);
+	server->_flush_pending();
+	LocalVector<int32_t> excluded;
+	BpcExcludeScope exclude_scope(server, server->ctx, p_parameters.exclude, excluded);
 	Vector<Vector3> ft;
 	ft.push_back(p_parameters.from);
 	ft.push_back(p_parameters.to);

@@ -37,9 +37,10 @@ public:
 	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit);
 	virtual int intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
 	virtual int intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
-	virtual bool cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info = nullptr) override { BPC_UNSUPPORTED("cast_motion"); return false; }
+	virtual bool cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info = nullptr) override;
 	virtual bool collide_shape(const ShapeParameters &p_parameters, Vector3 *r_results, int p_result_max, int &r_result_count) override;
-	virtual bool rest_info(const ShapeParameters &p_parameters, ShapeRestInfo *r_info) override { BPC_UNSUPPORTED("rest_info"); return false; }
+	virtual bool rest_info(const ShapeParameters &p_parameters, ShapeRestInfo *r_info) override;
+	void _fill_rest_info(const bpc_rest_info &p_info, ShapeRestInfo *r_info) const;
 	virtual Vector3 get_closest_point_to_object_volume(RID p_object, const Vector3 p_point) const override { BPC_UNSUPPORTED("get_closest_point_to_object_volume"); return p_point; }
 };
 
@@ -201,6 +202,15 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	void _body_call_queries(Body *p_body);
 	void _body_push(Body *p_body);
 	const float *_body_cached_state(const Body *p_body);
+
+public:
+	// body slot of a RID for the query exclude lists (-1: not a body, or not in a space yet)
+	int32_t body_slot_of(const RID &p_rid) const {
+		const Body *b = body_owner.get_or_null(p_rid);
+		return b ? b->slot : -1;
+	}
+
+private:
 	const bpc_contact *_body_contacts(const Body *p_body, int &r_count);
 	bool _body_mass_world(const Body *p_body, Basis &r_iinv, Vector3 &r_com, real_t &r_inv_mass) const;
 

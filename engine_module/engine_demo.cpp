@@ -332,6 +332,42 @@ int main(int argc, char **argv) {
 		}
 		printf("%s[%d, %d, %.9g, %.9g, %.9g]", i ? ", " : "", hit ? 1 : 0, idx, hit ? rr.position.x : 0.0, hit ? rr.position.y : 0.0, hit ? rr.position.z : 0.0);
 	}
+	// cast_motion and rest_info through the RID API: a sphere dropped from above each of the first bodies with that body excluded
+	// (so it lands on whatever lies under it), and the same sphere resting at the body's own place
+	printf("], \"casts\": [");
+	RID probe = ps->sphere_shape_create();
+	ps->shape_set_data(probe, 0.3f);
+	for (int i = 0; ds && i < n_rays; i++) {
+		Transform3D t = freed[i] ? Transform3D() : Transform3D(ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM));
+		PhysicsDirectSpaceState3D::ShapeParameters sp;
+		sp.shape_rid = probe;
+		sp.transform = Transform3D(Basis(), Vector3(t.origin.x, 30.0, t.origin.z));
+		sp.motion = Vector3(0, -31.0, 0);
+		if (!freed[i]) {
+			sp.exclude.insert(body_r[i]);
+		}
+		real_t safe = 1, unsafe = 1;
+		PhysicsDirectSpaceState3D::ShapeRestInfo ci;
+		ds->cast_motion(sp, safe, unsafe, &ci);
+		int idx = -1, ridx = -1;
+		for (size_t k = 0; k < body_r.size(); k++) {
+			if (ci.rid.is_valid() && body_r[k] == ci.rid) {
+				idx = (int)k;
+			}
+		}
+		PhysicsDirectSpaceState3D::ShapeParameters rp;
+		rp.shape_rid = probe;
+		rp.transform = Transform3D(Basis(), t.origin);
+		rp.margin = 0.05;
+		PhysicsDirectSpaceState3D::ShapeRestInfo ri;
+		bool rest = ds->rest_info(rp, &ri);
+		for (size_t k = 0; rest && k < body_r.size(); k++) {
+			if (body_r[k] == ri.rid) {
+				ridx = (int)k;
+			}
+		}
+		printf("%s[%.9g, %.9g, %d, %d, %.9g, %.9g, %.9g]", i ? ", " : "", (double)safe, (double)unsafe, idx, ridx, rest ? ri.point.x : 0.0, rest ? ri.point.y : 0.0, rest ? ri.point.z : 0.0);
+	}
 	printf("]}\n");
 	fflush(stdout);
 	ps->finish();

@@ -235,7 +235,7 @@ int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order);
  * one space -- closest hit along each segment, bodies whose collision layer meets collision_mask, a shape the ray starts
  * inside is ignored unless BPC_RAY_HIT_FROM_INSIDE.  from_to: n x (from xyz, to xyz), host; out: n records, host.
  * `body` is the body slot (what the engine module maps back to a RID / ObjectID), -1 for a miss.
- * Not in this round: exclude lists, areas, pick_ray, face_index (no concave shapes yet). */
+ * Exclude lists: bpc_space_set_query_exclude below.  Not built: areas, pick_ray, face_index (no concave shapes yet). */
 typedef struct bpc_ray_result {
     int32_t hit;
     int32_t body;
@@ -256,17 +256,45 @@ int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *
 
 /* PhysicsDirectSpaceState3D::intersect_shape (servers/physics_server_3d.h:183-205; implementation
  * modules/bradot_physics_3d/bradot_space_3d.cpp:208-262), batched: query i is shape handle shapes[i] (from bpc_shape_create*)
- * placed at xforms[i] (12 floats, basis rows + origin); the answer lists the bodies whose shape it overlaps (margin 0).
+ * placed at xforms[i] (12 floats, basis rows + origin), grown by `margin` (0 = the plain routines, else the reference's withMargin
+ * variants); the answer lists the bodies whose shape it overlaps.
  * Output layout as bpc_space_intersect_points. */
 int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
-                               int max_results, int32_t *out_counts, int32_t *out_bodies);
+                               float margin, int max_results, int32_t *out_counts, int32_t *out_bodies);
 
 /* PhysicsDirectSpaceState3D::collide_shape (servers/physics_server_3d.h; implementation
- * modules/bradot_physics_3d/bradot_space_3d.cpp:383-431), batched, margin 0: for each query shape the contact pairs with
+ * modules/bradot_physics_3d/bradot_space_3d.cpp:383-431), batched: for each query shape (grown by `margin`) the contact pairs with
  * the bodies it overlaps.  out_points: n x max_results x 6 (point on the query shape, point on the body), max_results <= 32;
  * once full, a deeper pair replaces the least deep one (the reference's collecting callback). */
 int bpc_space_collide_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
-                             int max_results, int32_t *out_counts, float *out_points);
+                             float margin, int max_results, int32_t *out_counts, float *out_points);
+
+/* The bodies every space query of this context skips from now on (RayParameters / PointParameters / ShapeParameters ::exclude,
+ * servers/physics_server_3d.h:139-201; P3D/bradot_space_3d.cpp:86,151,233,294,408,540).  n = 0 clears the list. */
+int bpc_space_set_query_exclude(bpc_context *ctx, const int32_t *bodies, int n);
+
+/* PhysicsDirectSpaceState3D::rest_info (P3D/bradot_space_3d.cpp:513-569), batched: the deepest contact of query shape i, grown
+ * by max(margin, 0.0001), with the bodies it touches -- through the margin variants of the collision routines
+ * (P3D/bradot_collision_solver_3d_sat.cpp, withMargin) and the reference's rest callback (:453-511).  motions (n x 3, may be
+ * NULL) only sets the least depth a contact needs to count: min(|motion|, 0.05 margin).  `point` is on the body, `normal`
+ * points from the query shape to it, `linear_velocity` is the body's at that point. */
+typedef struct bpc_rest_info {
+    int32_t hit;
+    int32_t body;
+    float point[3];
+    float normal[3];
+    float linear_velocity[3];
+} bpc_rest_info;
+int bpc_space_rest_infos(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, const float *motions, float margin,
+                         unsigned collision_mask, bpc_rest_info *out);
+
+/* PhysicsDirectSpaceState3D::cast_motion (P3D/bradot_space_3d.cpp:264-381), batched: query shape i at xforms[i] travels along
+ * motions[i] (n x 3, world); out_fractions[i] = (closest safe, closest unsafe) fraction of the motion, (1, 1) when nothing is
+ * in the way; bodies the shape starts inside of are ignored.  The distance test is the reference's GJK (P3D/gjk_epa.cpp:216-542,
+ * 888-927) on the swept shape, eight bisection steps per candidate.  out_info (may be NULL) is the ShapeRestInfo the reference
+ * fills alongside: the body that stops the motion first, the closest point on it, the normal towards the query shape. */
+int bpc_space_cast_motions(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, const float *motions, float margin,
+                           unsigned collision_mask, float *out_fractions, bpc_rest_info *out_info);
 
 /* ---- utilities exposed for tests and tools */
 /* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */

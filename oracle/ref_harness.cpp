@@ -527,6 +527,104 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 			o[1 + k * 3 + 2] = res[k].z;
 		}
 	}
+	// rest_info (bradot_space_3d.cpp:513-569) with the same shapes and poses, margin 0.04 for every other query (the rest use the
+	// default 0 -> the 0.0001 floor), motion = 0.01 along the ray; cast_motion (:264-381) along half the ray.  Per query:
+	// rest: hit, body, point(3), normal(3), velocity(3); cast: safe, unsafe, hit, body, point(3), normal(3), velocity(3)
+	std::vector<float> rest(n * 11, 0.f), cast(n * 13, 0.f);
+	for (size_t i = 0; i < n; i++) {
+		Vector3 from(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]), to(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+		PhysicsDirectSpaceState3D::ShapeParameters sp;
+		sp.shape_rid = qshape[i % 3];
+		sp.transform = xf_from(&sxf[i * 12]);
+		sp.collision_mask = 0xffffffffu;
+		sp.margin = (i % 2) ? 0.04f : 0.0f;
+		sp.motion = (to - from).normalized() * 0.01f;
+		PhysicsDirectSpaceState3D::ShapeRestInfo ri;
+		float *o = &rest[i * 11];
+		o[1] = -1.f;
+		if (ds && ds->rest_info(sp, &ri)) {
+			auto it = rid_index.find(ri.rid);
+			o[0] = 1.f;
+			o[1] = it == rid_index.end() ? -1.f : (float)it->second;
+			o[2] = ri.point.x; o[3] = ri.point.y; o[4] = ri.point.z;
+			o[5] = ri.normal.x; o[6] = ri.normal.y; o[7] = ri.normal.z;
+			o[8] = ri.linear_velocity.x; o[9] = ri.linear_velocity.y; o[10] = ri.linear_velocity.z;
+		}
+		sp.margin = 0.0f;
+		sp.motion = (to - from) * 0.5f;
+		real_t safe = 1, unsafe = 1;
+		PhysicsDirectSpaceState3D::ShapeRestInfo ci;
+		ci.rid = RID();
+		float *c = &cast[i * 13];
+		c[3] = -1.f;
+		if (ds) {
+			ds->cast_motion(sp, safe, unsafe, &ci);
+		}
+		c[0] = safe;
+		c[1] = unsafe;
+		if (ci.rid.is_valid()) {
+			auto it = rid_index.find(ci.rid);
+			c[2] = 1.f;
+			c[3] = it == rid_index.end() ? -1.f : (float)it->second;
+			c[4] = ci.point.x; c[5] = ci.point.y; c[6] = ci.point.z;
+			c[7] = ci.normal.x; c[8] = ci.normal.y; c[9] = ci.normal.z;
+			c[10] = ci.linear_velocity.x; c[11] = ci.linear_velocity.y; c[12] = ci.linear_velocity.z;
+		}
+	}
+	d.arr("shape_rest", step, "f4", { (uint64_t)n, 11 }, rest.data(), rest.size() * 4);
+	d.arr("shape_cast", step, "f4", { (uint64_t)n, 13 }, cast.data(), cast.size() * 4);
+	// exclude lists (RayParameters / ShapeParameters ::exclude): the rays and the shape intersections again with every body that
+	// the first pass hit excluded -- rays: hit, body; shapes: count + up to 8 bodies
+	std::vector<int32_t> ex_r(n * 2, -1), ex_s(n * 9, -1);
+	for (size_t i = 0; i < n; i++) {
+		PhysicsDirectSpaceState3D::RayParameters rp;
+		rp.from = Vector3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]);
+		rp.to = Vector3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+		rp.collision_mask = 0xffffffffu;
+		if (out[i * 8 + 0] != 0.f && out[i * 8 + 1] >= 0.f) {
+			rp.exclude.insert(w.bodies[(int)out[i * 8 + 1]]);
+		}
+		PhysicsDirectSpaceState3D::RayResult rr;
+		bool hit = ds && ds->intersect_ray(rp, rr);
+		ex_r[i * 2] = hit ? 1 : 0;
+		if (hit) {
+			auto it = rid_index.find(rr.rid);
+			ex_r[i * 2 + 1] = it == rid_index.end() ? -1 : it->second;
+		}
+		PhysicsDirectSpaceState3D::ShapeParameters sp;
+		sp.shape_rid = qshape[i % 3];
+		sp.transform = xf_from(&sxf[i * 12]);
+		sp.collision_mask = 0xffffffffu;
+		if (sq[i * 9] > 0 && sq[i * 9 + 1] >= 0) {
+			sp.exclude.insert(w.bodies[sq[i * 9 + 1]]);
+		}
+		PhysicsDirectSpaceState3D::ShapeResult sr[8];
+		int cc = ds ? ds->intersect_shape(sp, sr, 8) : 0;
+		ex_s[i * 9] = cc;
+		for (int k = 0; k < cc; k++) {
+			auto it = rid_index.find(sr[k].rid);
+			ex_s[i * 9 + 1 + k] = it == rid_index.end() ? -1 : it->second;
+		}
+	}
+	// intersect_shape again with ShapeParameters::margin = 0.05 (the withMargin routines as a yes / no test)
+	std::vector<int32_t> sqm(n * 9, -1);
+	for (size_t i = 0; i < n; i++) {
+		PhysicsDirectSpaceState3D::ShapeParameters sp;
+		sp.shape_rid = qshape[i % 3];
+		sp.transform = xf_from(&sxf[i * 12]);
+		sp.collision_mask = 0xffffffffu;
+		sp.margin = 0.05f;
+		PhysicsDirectSpaceState3D::ShapeResult sr[8];
+		int cc = ds ? ds->intersect_shape(sp, sr, 8) : 0;
+		sqm[i * 9] = cc;
+		for (int k = 0; k < cc; k++) {
+			auto it = rid_index.find(sr[k].rid);
+			sqm[i * 9 + 1 + k] = it == rid_index.end() ? -1 : it->second;
+		}
+	}
+	d.arr("shape_queries_margin", step, "i4", { (uint64_t)n, 9 }, sqm.data(), sqm.size() * 4);
+	d.arr("rays_excl", step, "i4", { (uint64_t)n, 2 }, ex_r.data(), ex_r.size() * 4);
+	d.arr("shapes_excl", step, "i4", { (uint64_t)n, 9 }, ex_s.data(), ex_s.size() * 4);
 	d.arr("shape_collide", step, "f4", { (uint64_t)n, 1 + 16 * 6 }, cs.data(), cs.size() * 4);
 	d.arr("shape_queries", step, "i4", { (uint64_t)n, 9 }, sq.data(), sq.size() * 4);
 	d.arr("shape_query_xf", step, "f4", { (uint64_t)n, 12 }, sxf.data(), sxf.size() * 4);

@@ -40,6 +40,20 @@ def test_engine_module_matches_direct_c_abi(tmp_path):
     ft[:, 0], ft[:, 1], ft[:, 2] = direct[:n, 0], 30.0, direct[:n, 2]
     ft[:, 3], ft[:, 4], ft[:, 5] = direct[:n, 0], -1.0, direct[:n, 2]
     hit, body, pos, _ = ps.intersect_rays(ft)
+    # cast_motion (with an exclude list) and rest_info through the RID API == the C-ABI calls on the same state
+    casts = np.array(out["casts"], np.float64)
+    probe = ps.sphere_shape_create(0.3)
+    eye = np.array([1, 0, 0, 0, 1, 0, 0, 0, 1], np.float32)
+    for i in range(n):
+        ps.set_query_exclude([i])
+        fr, info = ps.cast_motions([probe], np.concatenate([eye, [direct[i, 0], 30.0, direct[i, 2]]]).astype(np.float32), [[0, -31.0, 0]])
+        assert np.array_equal(casts[i, 0:2].astype(np.float32), fr[0]) and int(casts[i, 2]) == (info["body"][0] if info["hit"][0] else -1), i
+        assert 0 < fr[0, 0] < 1 and info["body"][0] != i
+        ps.set_query_exclude([])
+        rest = ps.rest_infos([probe], np.concatenate([eye, direct[i]]).astype(np.float32), margin=0.05)
+        assert int(casts[i, 3]) == (rest["body"][0] if rest["hit"][0] else -1), i
+        if rest["hit"][0]:
+            assert np.array_equal(casts[i, 4:7].astype(np.float32), rest["point"][0])
     ps.finish()
     assert n == min(16, len(sc.bodies)) and hit.all() and np.array_equal(eng_rays[:, 0] != 0, hit)
     assert np.array_equal(eng_rays[:, 1].astype(np.int64), body.astype(np.int64))

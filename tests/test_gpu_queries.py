@@ -108,7 +108,8 @@ def test_intersect_points_against_the_reference():
 
 def test_intersect_shapes_against_the_reference():
     """intersect_shape: spheres, boxes and capsules placed at 3 000 poses (the harness's, dumped as "shape_query_xf") in a
-    mixed pile and in a hull pile; the set of overlapped bodies equals the reference's."""
+    mixed pile and in a hull pile; the set of overlapped bodies equals the reference's -- with margin 0 (the plain collision
+    routines) and with margin 0.05 (the withMargin ones)."""
     parity_needed()
     for sc, seed in ((scenes.mixed_pile(5, half=3.5), 12), (scenes.convex_pile(4), 13)):
         rays = _rays(3000, seed, 3.4, 4.0)
@@ -117,10 +118,10 @@ def test_intersect_shapes_against_the_reference():
         handles = np.array([ps.sphere_shape_create(0.35), ps.box_shape_create((0.3, 0.2, 0.25)), ps.capsule_shape_create(0.2, 0.9)], np.int32)
         shape_of = handles[np.arange(len(rays)) % 3]
         overlaps = 0
-        for k in (1, 30, 59):
+        for k, margin in ((1, 0.0), (30, 0.0), (59, 0.0), (30, 0.05), (59, 0.05)):
             parity.load_state(ps, dump, k)
-            counts, bodies = ps.intersect_shapes(shape_of, dump[("shape_query_xf", k)], max_results=8)
-            ref = dump[("shape_queries", k)]
+            counts, bodies = ps.intersect_shapes(shape_of, dump[("shape_query_xf", k)], max_results=8, margin=margin)
+            ref = dump[("shape_queries_margin" if margin else "shape_queries", k)]
             differ = 0
             for i in range(len(rays)):
                 if ref[i, 0] >= 8 or counts[i] >= 8:
@@ -167,4 +168,110 @@ def test_collide_shapes_against_the_reference():
             pairs_seen += rc
         assert differ <= len(rays) // 500, (k, differ)
     assert pairs_seen > 1000
+    ps.finish()
+
+
+def _shape_queries(ps, rays):
+    handles = np.array([ps.sphere_shape_create(0.35), ps.box_shape_create((0.3, 0.2, 0.25)), ps.capsule_shape_create(0.2, 0.9)], np.int32)
+    return handles[np.arange(len(rays)) % 3]
+
+
+def test_rest_info_against_the_reference():
+    """rest_info (bradot_space_3d.cpp:513-569; the withMargin collision routines + the rest callback): same query shapes and
+    poses as above, margin 0.04 on every other query and the 0.0001 floor on the rest.  Hit / no hit agrees except where a
+    contact is within rounding of the least allowed depth; where both hit the same body, point and normal to 1e-4."""
+    parity_needed()
+    for sc, seed in ((scenes.mixed_pile(5, half=3.5), 21), (scenes.convex_pile(4), 22)):
+        rays = _rays(3000, seed, 3.4, 4.0)
+        _, dump = parity.run_oracle(sc, 60, dump_from=0, dump_every=1, rays=rays)
+        ps = parity.new_server(sc, dump)
+        shape_of = _shape_queries(ps, rays)
+        d = rays[:, 3:6] - rays[:, 0:3]
+        motions = (d / np.linalg.norm(d, axis=1, keepdims=True) * np.float32(0.01)).astype(np.float32)
+        odd = np.arange(len(rays)) % 2 == 1
+        hits = 0
+        for k in (1, 30, 59):
+            parity.load_state(ps, dump, k)
+            xf = dump[("shape_query_xf", k)]
+            out = np.zeros(len(rays), server.REST_INFO_DT)
+            out[odd] = ps.rest_infos(shape_of[odd], xf[odd], motions[odd], margin=0.04)
+            out[~odd] = ps.rest_infos(shape_of[~odd], xf[~odd], motions[~odd], margin=0.0)
+            ref = dump[("shape_rest", k)]
+            rhit = ref[:, 0] > 0
+            same = (out["hit"] > 0) == rhit
+            assert same.mean() > 0.998, (k, int((~same).sum()))
+            both = (out["hit"] > 0) & rhit
+            agree = out["body"][both] == ref[both, 1].astype(np.int32)
+            assert agree.mean() > 0.99, (k, int((~agree).sum()))       # two bodies equally deep: either may be "the deepest"
+            sel = np.nonzero(both)[0][agree]
+            close = (np.abs(out["point"][sel] - ref[sel, 2:5]).max(axis=1) < POS_TOL) & (np.abs(out["normal"][sel] - ref[sel, 5:8]).max(axis=1) < NRM_TOL)
+            assert close.mean() > 0.995, (k, int((~close).sum()))      # same body, two contacts equally deep (a box lying flat)
+            assert np.max(np.abs(out["linear_velocity"][sel][close] - ref[sel, 8:11][close])) < 1e-3
+            hits += len(sel)
+        assert hits > 1500
+        ps.finish()
+
+
+def test_cast_motion_against_the_reference():
+    """cast_motion (bradot_space_3d.cpp:264-381; GJK distance on the swept shape, 8 bisection steps): the (safe, unsafe)
+    fractions are dyadic numbers chosen by distance tests, so they either equal the reference's exactly or -- where a test sits
+    within GJK's own 1e-4 accuracy of touching -- differ by a bisection step, or by a whole obstacle when that test was the
+    "starts inside, ignore it" one; the stopping body and the closest point on it agree."""
+    parity_needed()
+    for sc, seed in ((scenes.mixed_pile(5, half=3.5), 23), (scenes.convex_pile(4), 24)):
+        rays = _rays(3000, seed, 3.4, 4.0)
+        _, dump = parity.run_oracle(sc, 60, dump_from=0, dump_every=1, rays=rays)
+        ps = parity.new_server(sc, dump)
+        shape_of = _shape_queries(ps, rays)
+        motions = ((rays[:, 3:6] - rays[:, 0:3]) * np.float32(0.5)).astype(np.float32)
+        stopped = 0
+        for k in (1, 30, 59):
+            parity.load_state(ps, dump, k)
+            fr, info = ps.cast_motions(shape_of, dump[("shape_query_xf", k)], motions)
+            ref = dump[("shape_cast", k)]
+            exact = np.all(fr == ref[:, 0:2], axis=1)
+            assert exact.mean() > 0.99, (k, int((~exact).sum()), np.abs(fr - ref[:, 0:2]).max())
+            both = exact & (info["hit"] > 0) & (ref[:, 2] > 0)
+            assert np.array_equal((info["hit"] > 0)[exact], (ref[:, 2] > 0)[exact])
+            agree = info["body"][both] == ref[both, 3].astype(np.int32)
+            assert agree.mean() > 0.99, (k, int((~agree).sum()))
+            sel = np.nonzero(both)[0][agree]
+            close = np.abs(info["point"][sel] - ref[sel, 4:7]).max(axis=1) < 2e-3    # closest points of GJK: its accuracy is 1e-4 relative
+            assert close.mean() > 0.98, (k, int((~close).sum()))
+            stopped += int(((fr[:, 0] < 1) & exact).sum())
+        assert stopped > 500
+        ps.finish()
+
+
+def test_query_exclude_lists_against_the_reference():
+    """RayParameters / ShapeParameters ::exclude: every ray and shape query again with the body its first answer named excluded
+    (the harness does the same through the reference's exclude sets)."""
+    parity_needed()
+    sc = scenes.mixed_pile(5, half=3.5)
+    rays = _rays(600, 31, 3.4, 4.0)
+    _, dump = parity.run_oracle(sc, 40, dump_from=0, dump_every=1, rays=rays)
+    ps = parity.new_server(sc, dump)
+    shape_of = _shape_queries(ps, rays)
+    k = 39
+    parity.load_state(ps, dump, k)
+    ref_r, ref_s, first_r, first_s = dump[("rays_excl", k)], dump[("shapes_excl", k)], dump[("rays", k)], dump[("shape_queries", k)]
+    xf = dump[("shape_query_xf", k)]
+    ray_bad = shape_bad = changed = 0
+    for i in range(len(rays)):
+        ex = [int(first_r[i, 1])] if first_r[i, 0] > 0 and first_r[i, 1] >= 0 else []
+        ps.set_query_exclude(ex)
+        hit, body, _, _ = ps.intersect_rays(rays[i:i + 1])
+        ray_bad += bool(hit[0]) != bool(ref_r[i, 0]) or (hit[0] and body[0] != ref_r[i, 1])
+        changed += bool(ex) and (not hit[0] or body[0] != ex[0])
+        ex = [int(first_s[i, 1])] if first_s[i, 0] > 0 and first_s[i, 1] >= 0 else []
+        ps.set_query_exclude(ex)
+        counts, bodies = ps.intersect_shapes(shape_of[i:i + 1], xf[i:i + 1], max_results=8)
+        if ref_s[i, 0] < 8 and counts[0] < 8:
+            shape_bad += set(bodies[0, :counts[0]].tolist()) != set(ref_s[i, 1:1 + ref_s[i, 0]].tolist())
+        assert not ex or ex[0] not in bodies[0, :counts[0]]
+    ps.set_query_exclude([])
+    assert ray_bad <= 1 and shape_bad <= 1, (ray_bad, shape_bad)
+    assert changed > 100
+    hit, body, _, _ = ps.intersect_rays(rays)
+    assert np.array_equal(hit, first_r[:, 0] > 0) or (hit != (first_r[:, 0] > 0)).sum() <= 1       # the list is cleared again
     ps.finish()
