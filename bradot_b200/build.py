@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libbradot_physics_cuda.so")
 SOURCES = ["bpc_api.cu", "bpc_bodies.cu", "bpc_step.cu", "k_sort.cu", "k_integrate.cu", "k_broadphase.cu", "k_graph.cu",
-           "k_narrowphase.cu", "k_solver.cu", "k_queries.cu", "k_query_shapes.cu"]
+           "k_narrowphase.cu", "k_solver.cu", "k_queries.cu", "k_query_shapes.cu", "k_areas.cu"]
 # -fmad=false: the reference is built with -ffp-contract=off; structural comparisons must agree bit for bit
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-O2"]

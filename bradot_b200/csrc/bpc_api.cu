@@ -47,6 +47,8 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
     ctx->meta.free_(); ctx->io_slots.free_(); ctx->shape_id.free_(); ctx->shape_p.free_(); ctx->np_work.free_(); ctx->np_cwork.free_(); ctx->staging.free_(); ctx->a_range.free_(); ctx->a_range_cur.free_(); ctx->jsetup.free_(); ctx->items.free_(); ctx->npairs.free_(); ctx->tree_items.free_(); ctx->kin.free_(); ctx->kin_ids.free_(); ctx->ccd_ids.free_();
     ctx->island.free_(); ctx->island_flag.free_(); ctx->shapes.free_(); ctx->meshes.free_(); ctx->mverts.free_();
     ctx->mplanes.free_(); ctx->medges.free_(); ctx->mfaces.free_(); ctx->mindex.free_(); ctx->d_spaces.free_();
+    ctx->d_areas.free_(); ctx->area_list.free_(); ctx->area_start.free_(); ctx->body_area_cnt.free_(); ctx->body_area.free_(); ctx->area_events.free_();
+    ctx->q_exclude.free_();
     ctx->keys.free_(); ctx->keys_alt.free_(); ctx->vals.free_(); ctx->vals_alt.free_(); ctx->hist.free_();
     ctx->leaf_min.free_(); ctx->leaf_max.free_(); ctx->nodes.free_(); ctx->node_parent.free_(); ctx->node_flag.free_(); ctx->node_maxleaf.free_();
     ctx->big_items.free_(); ctx->big_start.free_(); ctx->bounds.free_(); ctx->counters.free_(); ctx->pair_keys_raw.free_();

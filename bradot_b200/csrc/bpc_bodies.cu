@@ -290,6 +290,7 @@ static int write_body_slots(bpc_context *ctx, const uint32_t *slots, const bpc_b
         ctx->h_big[slot] = (d.mode == MODE_STATIC && sh.meta.x == SH_PLANE) ? 1 : 0;
         ctx->h_ccd[slot] = (d.flags & 2u) ? 1 : 0;
         ctx->h_dead[slot] = 0;
+        if (!keep_state && !ctx->h_areas.empty()) ctx->area_reset_slots.push_back(slot); // ... and stands in no area yet
         if (!keep_state && slot < ctx->h_report_cap.size() && ctx->h_report_cap[slot]) { // a new body in a reused slot reports nothing
             ctx->h_report_cap[slot] = 0;
             ctx->report_dirty = true;
@@ -492,6 +493,7 @@ extern "C" int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n)
     }
     if (s.empty()) return 0;
     if (bpc_resolve_step(ctx)) return -1;
+    if (bpc_areas_body_gone(ctx, s)) return -1; // the areas it stood in are told (the pair objects' destructors)
     cudaStream_t st = ctx->stream;
     // No body is woken: the reference unpairs the body first (set_space(nullptr)), so by the time its shapes go and
     // _shapes_changed() calls wakeup_neighbours() its constraint map is empty -- a sleeping box on top of a freed one sleeps on.

@@ -117,6 +117,30 @@ struct SpaceParams {
     int alive = 1;  // 0 after bpc_space_destroy
 };
 
+// An area (BradotArea3D, bradot_area_3d.h:46-70): a shape that bodies overlap, not collide with.  `xf` is the area's own
+// transform (point gravity is given in its space), `sxf` the world transform of its shape.
+#define AREA_SLOTS 8u
+#define AREA_ATTACHED 0x80000000u
+#define AF_MONITORABLE 1u
+#define AF_MONITOR_CB 2u
+#define AF_GRAVITY_POINT 4u
+#define AF_AREA_MONITOR_CB 8u
+#define AF_ALIVE 0x100u
+#define AF_MOVED 0x200u
+#define AREA_EVENT_CAP (1u << 20)
+struct AreaRec {
+    float4 x0, x1, x2, xo;   // area transform: basis rows, origin
+    float4 s0, s1, s2, so;   // area transform * shape transform
+    float4 shape_p;          // shape parameters (hull: mesh index in x)
+    uint32_t shape_type, space, layer, mask;
+    uint32_t flags;
+    int32_t priority;
+    uint32_t gravity_mode, lin_damp_mode;
+    uint32_t ang_damp_mode;
+    float gravity, point_unit_distance, lin_damp;
+    float4 gravity_vector;   // w = angular damp
+};
+
 // Solver bins: islands whose root index shares a block of BIN_BLOCK body indices; one small CTA sweeps a bin whose dynamic bodies
 // span fewer than BIN_MAX_BODIES indices (their velocity records sit in shared memory) and that has at most BIN_MAX_CONS
 // constraints.
@@ -295,6 +319,17 @@ struct bpc_context {
     DevBuf<uint32_t> report_overflow_body;
     std::vector<uint32_t> h_report_cap;
     uint32_t report_total = 0, n_reporting = 0;
+    // areas (k_areas.cu): the table, the areas of each space, what each body stands in
+    std::vector<AreaRec> h_areas;
+    DevBuf<AreaRec> d_areas;
+    DevBuf<uint32_t> area_list, area_start; // area indices grouped by space; offsets per space (n_spaces + 1)
+    DevBuf<uint32_t> body_area_cnt, body_area; // per body: how many areas it overlaps, which (AREA_SLOTS each, bit 31 = attached)
+    DevBuf<uint4> area_events;                // (area, body, status, 0) of the last step
+    std::vector<uint4> h_area_events_pending; // events raised outside a step (a body or an area went away)
+    std::vector<uint32_t> area_reset_slots;   // body slots reused since the last step: their area lists start empty
+    uint32_t body_area_cap = 0;               // bodies the per-body arrays are sized for
+    bool areas_dirty = false, areas_moved = false;
+    uint32_t n_areas_alive = 0;
     bool report_dirty = false;
 
     // constraints / solver
@@ -328,7 +363,7 @@ struct bpc_context {
 };
 
 enum { CNT_PAIRS = 0, CNT_CONS = 1, CNT_COLORS = 2, CNT_UNCOLORED = 3, CNT_ACTIVE = 4, CNT_ISLANDS = 5, CNT_CONTACTS = 6,
-       CNT_OVERFLOW = 7, CNT_GROUPS = 8 /* colours on the grid-barrier path */, CNT_BARRIER_CONS = 9, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_REPORT_OVERFLOW = 13, CNT_ROUND = 20 /* 3 slots */, CNT_N = 32 };
+       CNT_OVERFLOW = 7, CNT_GROUPS = 8 /* colours on the grid-barrier path */, CNT_BARRIER_CONS = 9, CNT_ACTIVE_CONTACTS = 10, CNT_WORK = 11, CNT_CWORK = 12, CNT_REPORT_OVERFLOW = 13, CNT_AREA_EVENTS = 14, CNT_AREA_OVERFLOW = 15, CNT_ROUND = 20 /* 3 slots */, CNT_N = 32 };
 
 #define REPORT_OVERFLOW_CAP 65536u // reported contacts beyond their bodies' caps held per step for the deepest-N merge
 
@@ -405,6 +440,9 @@ int bpc_launch_broadphase(bpc_context *ctx);
 int bpc_build_tree(bpc_context *ctx); // LBVH over the current stored boxes (also used by the space queries)
 int bpc_launch_islands(bpc_context *ctx);
 int bpc_launch_narrowphase(bpc_context *ctx);
+int bpc_flush_area_tables(bpc_context *ctx);                                      // k_areas.cu
+int bpc_launch_areas(bpc_context *ctx);
+int bpc_areas_body_gone(bpc_context *ctx, const std::vector<uint32_t> &slots);
 int bpc_launch_solver(bpc_context *ctx, float dt);
 int bpc_launch_joint_setup(bpc_context *ctx, float dt);
 int bpc_launch_sleep(bpc_context *ctx, float dt);

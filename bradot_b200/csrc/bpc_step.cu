@@ -148,6 +148,7 @@ extern "C" int bpc_step(bpc_context *ctx, float dt) {
     ctx->launches = 0;
     BPC_CHECK(cudaMemsetAsync(ctx->counters.p, 0, CNT_N * sizeof(uint32_t), st));
     if (bpc_flush_report_tables(ctx)) return -1;
+    if (bpc_flush_area_tables(ctx)) return -1;
     if (ctx->n_reporting) {
         k_report_reset<<<nblk(ctx->n_bodies, 256), 256, 0, st>>>(ctx->n_bodies, ctx->meta.p, ctx->report_count.p);
         ctx->launches += 1;
@@ -163,6 +164,7 @@ extern "C" int bpc_step(bpc_context *ctx, float dt) {
     if (bpc_launch_islands(ctx)) return -1;
     STAGE(3);
     if (bpc_launch_narrowphase(ctx)) return -1;
+    if (bpc_launch_areas(ctx)) return -1;
     if (bpc_launch_joint_setup(ctx, dt)) return -1;
     uint32_t np = ctx->n_pairs[ctx->cur];
     if (np) { // (folding this count into k_con_collect was measured: two atomic streams on one line, 0.39 ms instead of 0.14 + 0.13)

@@ -16,10 +16,95 @@
 
 __device__ __forceinline__ M3 load_basis(const BodyXf &x) { return M3(f4v(x.r0), f4v(x.r1), f4v(x.r2)); }
 
+// BradotArea3D::compute_gravity (bradot_area_3d.cpp:312-332)
+__device__ __forceinline__ V3 area_gravity(const AreaRec &ar, V3 position) {
+    V3 gv = f4v(ar.gravity_vector);
+    if (ar.flags & AF_GRAVITY_POINT) {
+        X3 ax(M3(f4v(ar.x0), f4v(ar.x1), f4v(ar.x2)), f4v(ar.xo));
+        V3 v = xform(ax, gv) - position;
+        if (ar.point_unit_distance > 0) {
+            float v_length_sq = length_squared(v);
+            if (v_length_sq > 0) {
+                float gravity_strength = ar.gravity * ar.point_unit_distance * ar.point_unit_distance / v_length_sq;
+                return normalized(v) * gravity_strength;
+            }
+            return V3();
+        }
+        return normalized(v) * ar.gravity;
+    }
+    return gv * ar.gravity;
+}
+
+// The area loop of integrate_forces (bradot_body_3d.cpp:498-585): the areas attached to the body from the highest priority
+// down; each may add to or replace gravity, linear and angular damping, and may end the walk for that quantity.  What is
+// not settled by an area gets the space's default area on top.
+__device__ inline void area_overrides(const AreaRec *__restrict__ areas, const uint32_t *__restrict__ list, uint32_t cnt, V3 position,
+                                      const SpaceParams &sp, V3 &gravity, float &lin_damp, float &ang_damp) {
+    uint32_t idx[AREA_SLOTS];
+    int ac = 0;
+    for (uint32_t q = 0; q < cnt && q < AREA_SLOTS; q++) {
+        uint32_t e = list[q];
+        if (e & AREA_ATTACHED) idx[ac++] = e & ~AREA_ATTACHED;
+    }
+    // areas.sort() by priority (AreaCMP, bradot_area_3d.h:223-236); equal priorities: by index here
+    for (int i = 1; i < ac; i++) {
+        uint32_t v = idx[i];
+        int pv = areas[v].priority, j = i - 1;
+        while (j >= 0 && (areas[idx[j]].priority > pv || (areas[idx[j]].priority == pv && idx[j] > v))) {
+            idx[j + 1] = idx[j];
+            j--;
+        }
+        idx[j + 1] = v;
+    }
+    bool gravity_done = false, lin_done = false, ang_done = false, stopped = false;
+    gravity = V3();
+    lin_damp = 0.f;
+    ang_damp = 0.f;
+    for (int i = ac - 1; i >= 0 && !stopped; i--) {
+        const AreaRec ar = areas[idx[i]];
+        if (!gravity_done && ar.gravity_mode != 0u) {
+            V3 g = area_gravity(ar, position);
+            if (ar.gravity_mode == 1u || ar.gravity_mode == 2u) {
+                gravity += g;
+                gravity_done = ar.gravity_mode == 2u;
+            } else {
+                gravity = g;
+                gravity_done = ar.gravity_mode == 3u;
+            }
+        }
+        if (!lin_done && ar.lin_damp_mode != 0u) {
+            if (ar.lin_damp_mode == 1u || ar.lin_damp_mode == 2u) {
+                lin_damp += ar.lin_damp;
+                lin_done = ar.lin_damp_mode == 2u;
+            } else {
+                lin_damp = ar.lin_damp;
+                lin_done = ar.lin_damp_mode == 3u;
+            }
+        }
+        if (!ang_done && ar.ang_damp_mode != 0u) {
+            if (ar.ang_damp_mode == 1u || ar.ang_damp_mode == 2u) {
+                ang_damp += ar.gravity_vector.w;
+                ang_done = ar.ang_damp_mode == 2u;
+            } else {
+                ang_damp = ar.gravity_vector.w;
+                ang_done = ar.ang_damp_mode == 3u;
+            }
+        }
+        stopped = gravity_done && lin_done && ang_done;
+    }
+    if (!stopped) {
+        if (!gravity_done) gravity += V3(sp.gravity[0], sp.gravity[1], sp.gravity[2]);
+        if (!lin_done) lin_damp += sp.lin_damp;
+        if (!ang_done) ang_damp += sp.ang_damp;
+    }
+}
+
 __global__ void __launch_bounds__(IT_THREADS) k_integrate_forces(uint32_t n, float dt, BodyVel *__restrict__ vel,
                                                                  BodyProps *__restrict__ props, BodyForces *__restrict__ forces,
                                                                  const BodyMassW *__restrict__ massw, const uint4 *__restrict__ meta,
-                                                                 const SpaceParams *__restrict__ spaces, uint32_t *__restrict__ counters) {
+                                                                 const SpaceParams *__restrict__ spaces, uint32_t *__restrict__ counters,
+                                                                 const AreaRec *__restrict__ areas, const uint32_t *__restrict__ body_area_cnt,
+                                                                 const uint32_t *__restrict__ body_area, const BodyXf *__restrict__ xf) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     bool act = false;
     if (i < n) {
@@ -35,10 +120,14 @@ __global__ void __launch_bounds__(IT_THREADS) k_integrate_forces(uint32_t n, flo
             if (mode >= MODE_RIGID && !(flags & BF_OMIT_FORCE)) {
                 BodyForces f = forces[i];
                 BodyMassW mw = massw[i];
-                V3 gravity = V3(sp.gravity[0], sp.gravity[1], sp.gravity[2]) * p.iinv_gs.w;
-                // the body's own damping is added to the default area's (COMBINE) or takes its place (REPLACE), bradot_body_3d.cpp:586-606
-                float ld = (flags & BF_LIN_REPLACE) ? p.a0.w : sp.lin_damp + p.a0.w;
-                float ad = (flags & BF_ANG_REPLACE) ? p.a1.w : sp.ang_damp + p.a1.w;
+                V3 gravity = V3(sp.gravity[0], sp.gravity[1], sp.gravity[2]);
+                float area_ld = sp.lin_damp, area_ad = sp.ang_damp;
+                uint32_t ac = areas ? body_area_cnt[i] : 0u;
+                if (ac) area_overrides(areas, body_area + (size_t)i * AREA_SLOTS, ac, f4v(xf[i].o), sp, gravity, area_ld, area_ad);
+                gravity = gravity * p.iinv_gs.w;
+                // the body's own damping is added to the areas' (COMBINE) or takes its place (REPLACE), bradot_body_3d.cpp:586-606
+                float ld = (flags & BF_LIN_REPLACE) ? p.a0.w : area_ld + p.a0.w;
+                float ad = (flags & BF_ANG_REPLACE) ? p.a1.w : area_ad + p.a1.w;
                 V3 force = gravity * p.com_mass.w + f4v(f.force) + f4v(f.cforce);
                 V3 torque = f4v(f.torque) + f4v(f.ctorque);
                 float damp = 1.0f - dt * ld;
@@ -494,8 +583,11 @@ static inline uint32_t nblk(uint32_t n, uint32_t t) { return (n + t - 1) / t; }
 int bpc_launch_integrate_forces(bpc_context *ctx, float dt) {
     uint32_t n = ctx->n_bodies;
     if (!n) return 0;
+    const bool with_areas = ctx->n_areas_alive && ctx->body_area_cap >= n && ctx->d_areas.p;
     k_integrate_forces<<<nblk(n, IT_THREADS), IT_THREADS, 0, ctx->stream>>>(n, dt, ctx->vel.p, ctx->props.p, ctx->forces.p, ctx->massw.p,
-                                                                            ctx->meta.p, ctx->d_spaces.p, ctx->counters.p);
+                                                                            ctx->meta.p, ctx->d_spaces.p, ctx->counters.p,
+                                                                            with_areas ? ctx->d_areas.p : nullptr, ctx->body_area_cnt.p,
+                                                                            ctx->body_area.p, ctx->xf.p);
     ctx->launches += 1;
     uint32_t nc = (uint32_t)ctx->h_ccd_ids.size();
     if (nc) {

@@ -29,6 +29,13 @@ BODY_DT = np.dtype([
 # lower, limit bias, limit softness, limit relaxation, motor target velocity, motor max impulse); priority 0 = default (1)
 JOINT_DT = np.dtype([("type", "<u4"), ("body_a", "<u4"), ("body_b", "<u4"), ("flags", "<u4"),
                      ("fa", "<f4", 12), ("fb", "<f4", 12), ("params", "<f4", 8), ("priority", "<u4"), ("pad", "<u4", 3)])
+# bpc_area_desc as is.  flags: bit0 monitorable, bit1 body monitor callback (events), bit2 gravity is a point; override modes:
+# PhysicsServer3D::AreaSpaceOverrideMode (0 disabled, 1 combine, 2 combine-replace, 3 replace, 4 replace-combine)
+AREA_DT = np.dtype([("space", "<i4"), ("shape", "<i4"), ("flags", "<u4"), ("priority", "<i4"), ("xf", "<f4", 12), ("shape_xf", "<f4", 12),
+                    ("layer", "<u4"), ("mask", "<u4"), ("gravity_mode", "<i4"), ("linear_damp_mode", "<i4"), ("angular_damp_mode", "<i4"),
+                    ("gravity", "<f4"), ("gravity_vector", "<f4", 3), ("point_unit_distance", "<f4"), ("linear_damp", "<f4"),
+                    ("angular_damp", "<f4"), ("reserved", "<u4")])
+AREA_MONITORABLE, AREA_MONITOR_CB, AREA_GRAVITY_POINT = 1, 2, 4
 JOINT_NO_COLLIDE, JOINT_USE_LIMIT, JOINT_ENABLE_MOTOR, JOINT_HAS_PARAMS = 1, 2, 4, 8
 PIN_DEFAULTS = np.array([0.3, 1.0, 0.0, 0, 0, 0, 0, 0], np.float32)
 HINGE_DEFAULTS = np.array([0.3, -np.pi, np.pi, 0.3, 0.9, 1.0, 0.0, 0.0], np.float32)   # upper = -pi, lower = pi: the reference's "no limit"
@@ -51,6 +58,7 @@ class Scene:
         self.shapes = np.zeros(0, SHAPE_DT)
         self.bodies = np.zeros(0, BODY_DT)
         self.joints = np.zeros(0, JOINT_DT)
+        self.areas = np.zeros(0, AREA_DT)
         self.verts = np.zeros((0, 3), np.float32)
 
     # -- builders -------------------------------------------------------------
@@ -95,6 +103,22 @@ class Scene:
         self.joints = np.concatenate([self.joints, rec])
         return first
 
+    def add_areas(self, n, **fields):
+        rec = np.zeros(n, AREA_DT)
+        rec["xf"] = IDENT12
+        rec["shape_xf"] = IDENT12
+        rec["layer"] = 1
+        rec["mask"] = 1
+        rec["gravity"] = 9.80665          # BradotArea3D defaults, bradot_area_3d.h:50-57
+        rec["gravity_vector"] = (0, -1, 0)
+        rec["linear_damp"] = 0.1
+        rec["angular_damp"] = 0.1
+        for k, v in fields.items():
+            rec[k] = v
+        first = len(self.areas)
+        self.areas = np.concatenate([self.areas, rec])
+        return first
+
     def add_static_plane(self, normal, d, space=0):
         s = self.add_shape(SHAPE_PLANE, (normal[0], normal[1], normal[2], d))
         return self.add_bodies(1, mode=MODE_STATIC, shape=s, space=space, mass=1.0)
@@ -102,19 +126,20 @@ class Scene:
     # -- file I/O ---------------------------------------------------------------
     def write(self, path):
         hdr = struct.pack("<4sIIIIIIfI7I", b"BSCN", 2, self.n_spaces, len(self.shapes), len(self.bodies),
-                          len(self.joints), len(self.verts), float(self.dt), self.iterations, self.iter_step, *([0] * 6))
+                          len(self.joints), len(self.verts), float(self.dt), self.iterations, self.iter_step, len(self.areas), *([0] * 5))
         with open(path, "wb") as f:
             f.write(hdr)
             f.write(self.shapes.tobytes())
             f.write(self.bodies.tobytes())
             f.write(self.joints.tobytes())
             f.write(np.ascontiguousarray(self.verts, np.float32).tobytes())
+            f.write(self.areas.tobytes())
 
     @staticmethod
     def read(path):
         with open(path, "rb") as f:
             raw = f.read()
-        magic, ver, nsp, nsh, nb, nj, nv, dt, it, its = struct.unpack_from("<4sIIIIIIfII", raw, 0)
+        magic, ver, nsp, nsh, nb, nj, nv, dt, it, its, na = struct.unpack_from("<4sIIIIIIfIII", raw, 0)
         assert magic == b"BSCN" and ver == 2
         off = struct.calcsize("<4sIIIIIIfI7I")
         sc = Scene(nsp, dt, it)
@@ -126,6 +151,8 @@ class Scene:
         sc.joints = np.frombuffer(raw, JOINT_DT, nj, off).copy()
         off += nj * JOINT_DT.itemsize
         sc.verts = np.frombuffer(raw, "<f4", nv * 3, off).reshape(-1, 3).copy()
+        off += nv * 12
+        sc.areas = np.frombuffer(raw, AREA_DT, na, off).copy()
         return sc
 
 
@@ -601,4 +628,84 @@ def scripted_events_script():
     add(100, 9, 3, ())                               # free a box that is falling / resting on the platform
     add(110, 2, 5, (0.0,))                           # a sleeping box may no longer sleep: it wakes
     add(120, 11, 4, (0.0,))                          # wake the ball again
+    return ev
+
+
+def area_zones():
+    """Areas: bodies in free flight -- nothing ever touches, so a free run follows the reference to rounding --
+    (all masks are 0) falling through zones that override gravity and damping by priority, a point-gravity well, monitoring areas that report who
+    enters and leaves, a kinematic body carried through one, static bodies in a monitorable and in a plain area, a body on a
+    layer the areas do not see, a sleeping body an area is moved onto.  Script: area_zones_script()."""
+    sc = Scene(name="area_zones")
+    ball = sc.add_shape(SHAPE_SPHERE, (0.2,))
+    box = sc.add_shape(SHAPE_BOX, (0.2, 0.15, 0.25))
+    cap = sc.add_shape(SHAPE_CAPSULE, (0.15, 0.7))
+    zone = sc.add_shape(SHAPE_BOX, (1.0, 0.75, 1.0))        # area shapes
+    slab = sc.add_shape(SHAPE_BOX, (1.0, 0.3, 1.0))
+    well = sc.add_shape(SHAPE_SPHERE, (2.0,))
+    tube = sc.add_shape(SHAPE_CAPSULE, (0.8, 3.0))
+
+    def at(x, y, z, rot=0.0):
+        f = IDENT12.copy()
+        f[0], f[2], f[6], f[8] = np.cos(rot), np.sin(rot), -np.sin(rot), np.cos(rot)
+        f[9], f[10], f[11] = x, y, z
+        return f
+    # column A (x = 0): three shapes fall through an anti-gravity zone with a damping zone inside it
+    for k, (sh, y) in enumerate(((ball, 6.0), (box, 7.5), (cap, 9.0))):
+        sc.add_bodies(1, shape=sh, xf=at(0.9 * k - 0.9, y, 0.1 * k, 0.2 * k), angvel=(0.5 * k, 0.2, 0.1), flags=0)
+    sc.add_areas(1, shape=zone, xf=at(0.0, 3.0, 0.0), gravity_mode=3, gravity=4.0, gravity_vector=(0, 1, 0), flags=AREA_MONITOR_CB, priority=0)
+    sc.add_areas(1, shape=slab, xf=at(0.0, 3.2, 0.0, 0.3), linear_damp_mode=1, linear_damp=2.0, angular_damp_mode=3, angular_damp=3.0, priority=1)
+    # column B (x = 5): combine-replace sideways gravity of high priority over a replace zone of low priority
+    for k, (sh, y) in enumerate(((box, 6.0), (ball, 7.0))):
+        sc.add_bodies(1, shape=sh, xf=at(5.0, y, 0.3 * k), flags=0)
+    sc.add_areas(1, shape=zone, xf=at(5.0, 3.0, 0.0), gravity_mode=3, gravity=1.0, gravity_vector=(0, -1, 0), priority=0, flags=AREA_MONITOR_CB)
+    sc.add_areas(1, shape=zone, xf=at(5.0, 3.5, 0.0), gravity_mode=2, gravity=3.0, gravity_vector=(1, 0, 0), priority=5)
+    # column C (x = 10): a point-gravity well (replace-combine: the default gravity is added on top), unit distance 1
+    for k in range(3):
+        sc.add_bodies(1, shape=ball, xf=at(10.0 + 0.9 * k, 7.0 + k, 0.5 * k), linvel=(0.3, 0.0, 0.0), flags=0)
+    sc.add_areas(1, shape=well, xf=at(10.0, 3.0, 0.0), gravity_mode=4, gravity=6.0, gravity_vector=(0.0, 0.5, 0.0), point_unit_distance=1.0,
+                 flags=AREA_GRAVITY_POINT | AREA_MONITOR_CB)
+    # column D (x = 15): a monitorable, monitoring area with no override: a kinematic box is carried through it, a static box
+    # stands in it; next to it a plain monitoring area with a static box in it (they never pair)
+    sc.add_bodies(1, mode=MODE_KINEMATIC, shape=box, xf=at(12.0, 3.0, 0.0), linvel=(1.5, 0.0, 0.0), angvel=(0.0, 0.4, 0.0))
+    sc.add_bodies(1, mode=MODE_STATIC, shape=box, xf=at(15.3, 3.2, 0.2))
+    sc.add_bodies(1, mode=MODE_STATIC, shape=box, xf=at(20.0, 3.0, 0.0))
+    sc.add_areas(1, shape=tube, xf=at(15.0, 3.0, 0.0), flags=AREA_MONITORABLE | AREA_MONITOR_CB)
+    sc.add_areas(1, shape=zone, xf=at(20.0, 3.0, 0.0), flags=AREA_MONITOR_CB)
+    # column E (x = 25): a ball on layer 2 that the zone's mask does not see, one it does; a zone that only sees layer 4
+    sc.add_bodies(1, shape=ball, xf=at(25.0, 5.0, 0.0), layer=2, mask=2, flags=0)
+    sc.add_bodies(1, shape=ball, xf=at(25.5, 5.5, 0.0), flags=0)
+    sc.add_areas(1, shape=zone, xf=at(25.0, 3.0, 0.0), gravity_mode=3, gravity=0.0, flags=AREA_MONITOR_CB)
+    sc.add_areas(1, shape=zone, xf=at(25.0, 3.0, 0.0), mask=4, gravity_mode=3, gravity=50.0, flags=AREA_MONITOR_CB, priority=9)
+    # column F (x = 30): a body the script puts to sleep in mid-air at step 2 (the reference wakes every body on the first
+    # step after its shapes were added, so "asleep from the start" would not hold there); the script moves a zone onto it
+    sc.add_bodies(1, shape=box, xf=at(30.0, 3.0, 0.0), flags=1)
+    sc.add_areas(1, shape=zone, xf=at(30.0, 9.0, 0.0), gravity_mode=3, gravity=2.0, gravity_vector=(0, 1, 0), flags=AREA_MONITOR_CB)
+    # column G (x = 35): a ball that is freed while inside a monitoring zone, and a zone that is freed with a ball inside
+    sc.add_bodies(1, shape=ball, xf=at(35.0, 4.5, 0.0), flags=0)
+    sc.add_areas(1, shape=zone, xf=at(35.0, 3.0, 0.0), linear_damp_mode=3, linear_damp=8.0, flags=AREA_MONITOR_CB)
+    sc.add_bodies(1, shape=ball, xf=at(40.0, 4.5, 0.0), flags=0)
+    sc.add_areas(1, shape=zone, xf=at(40.0, 3.0, 0.0), gravity_mode=3, gravity=0.5, gravity_vector=(0, 1, 0), flags=AREA_MONITOR_CB)
+    sc.bodies["mask"] = 0          # no body collides with any other: free flight only (an area looks at the body's LAYER)
+    return sc
+
+
+def area_zones_script():
+    """(step, index, kind, 12 floats): kind 6 = area_set_transform(area index), 7 = free(area), 3 = free(body), 4 = sleeping."""
+    ev = []
+
+    def add(step, idx, kind, v=()):
+        row = np.zeros(12, np.float32)
+        row[:len(v)] = v
+        ev.append((step, idx, kind, row))
+    moved = IDENT12.copy()
+    moved[9], moved[10], moved[11] = 30.0, 3.3, 0.2
+    add(2, 13, 4, (1.0,))         # the box of column F is put to sleep where it is
+    add(40, 9, 6, moved)          # the zone of column F comes down onto the sleeping box: it is told although the box sleeps
+    add(60, 13, 4, (0.0,))        # ... and only when the box is woken does the override move it
+    add(55, 14, 3)                # free the ball of column G inside its zone: the zone hears it leave
+    add(50, 11, 7)                # free the last zone with its ball inside: the ball falls on under default gravity
+    away = IDENT12.copy()
+    away[9], away[10], away[11] = 5.0, 30.0, 0.0
+    add(70, 3, 6, away)           # the sideways zone of column B is taken away while bodies may still be in it
     return ev

@@ -46,6 +46,7 @@ EXPORTS = [
     "bpc_bodies_set_max_contacts_reported", "bpc_body_read_contacts", "bpc_contacts_capacity", "bpc_contacts_read",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
     "bpc_space_set_query_exclude", "bpc_space_rest_infos", "bpc_space_cast_motions",
+    "bpc_areas_create", "bpc_areas_write", "bpc_areas_destroy", "bpc_area_count", "bpc_area_events_read", "bpc_body_read_areas",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
 
@@ -113,6 +114,12 @@ def load_library(path=LIB_PATH):
     lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
     lib.bpc_space_collide_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
     lib.bpc_space_set_query_exclude.argtypes = [vp, vp, ci]
+    lib.bpc_areas_create.argtypes = [vp, vp, ci]
+    lib.bpc_areas_write.argtypes = [vp, ci, ci, vp]
+    lib.bpc_areas_destroy.argtypes = [vp, vp, ci]
+    lib.bpc_area_count.argtypes = [vp]
+    lib.bpc_area_events_read.argtypes = [vp, vp, ci]
+    lib.bpc_body_read_areas.argtypes = [vp, ci, vp, ci]
     lib.bpc_space_rest_infos.argtypes = [vp, ci, ci, vp, vp, vp, cf, ctypes.c_uint, vp]
     lib.bpc_space_cast_motions.argtypes = [vp, ci, ci, vp, vp, vp, cf, ctypes.c_uint, vp, vp]
     lib.bpc_synchronize.argtypes = [vp]
@@ -396,6 +403,33 @@ class PhysicsServerCUDA:
                                                       ctypes.c_float(margin), int(max_results), _ptr(counts), _ptr(pts)))
         return counts, pts
 
+    # -- areas ------------------------------------------------------------------------------------
+    def areas_create(self, records):
+        rec = np.ascontiguousarray(records, scenes.AREA_DT)
+        return self._check(self.lib.bpc_areas_create(self.ctx, _ptr(rec), len(rec)))
+
+    def areas_write(self, first, records):
+        """Any area_set_* on areas [first, first + n): the records again; the areas count as moved for the next step."""
+        rec = np.ascontiguousarray(records, scenes.AREA_DT)
+        self._check(self.lib.bpc_areas_write(self.ctx, int(first), len(rec), _ptr(rec)))
+
+    def areas_destroy(self, areas):
+        a = np.ascontiguousarray(areas, np.int32).reshape(-1)
+        self._check(self.lib.bpc_areas_destroy(self.ctx, _ptr(a), len(a)))
+
+    def area_events(self, max_events=65536):
+        """Enter / exit events since the last call: int32 (n, 3) = area, body, status (0 added, 1 removed)."""
+        out = np.zeros((max_events, 3), np.int32)
+        n = self._check(self.lib.bpc_area_events_read(self.ctx, _ptr(out), max_events))
+        return out[:min(n, max_events)]
+
+    def body_areas(self, slot):
+        """(areas the body stands in, which of them are attached as space overrides)."""
+        out = np.zeros(8, np.int32)
+        n = self._check(self.lib.bpc_body_read_areas(self.ctx, int(slot), _ptr(out), 8))
+        v = out[:min(n, 8)]
+        return v & 0x3FFFFFFF, (v & 0x40000000) != 0
+
     def set_query_exclude(self, bodies):
         """Bodies every following space query skips (the `exclude` list of the query parameters); empty clears."""
         b = np.ascontiguousarray(bodies, np.int32).reshape(-1)
@@ -464,6 +498,8 @@ class PhysicsServerCUDA:
             self.bodies_set_max_contacts_reported(first + idx, want[idx])
         if len(sc.joints):
             self.joints_create(sc.joints)
+        if len(getattr(sc, "areas", ())):
+            self.areas_create(sc.areas)
         return first
 
 

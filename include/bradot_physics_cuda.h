@@ -30,7 +30,10 @@ enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1 };
 typedef struct bpc_body_desc {
     /* flags: bit0 can_sleep, bit1 continuous collision detection, bit2 start asleep, bit4 / bit5 linear / angular damp mode
      * REPLACE (BODY_PARAM_*_DAMP_MODE, P3D/bradot_body_3d.cpp:586-606), bit6 omit force integration, bits 8..13 axis locks
-     * in PhysicsServer3D::BodyAxis order (body_set_axis_lock, P3D/bradot_body_3d.cpp:685-699) */
+     * in PhysicsServer3D::BodyAxis order (body_set_axis_lock, P3D/bradot_body_3d.cpp:685-699).
+     * bit2 is kept as given: the body sleeps until something wakes it.  (The reference would wake it on its first step:
+     * every body whose shapes were just added has a pending shape update, and BradotBody3D::_shapes_changed ends in
+     * wakeup(), P3D/bradot_body_3d.cpp:343-347 -- there a body can only be put to sleep after that step.) */
     uint32_t space, mode, shape, flags;
     float xf[12];                       /* basis rows (9) then origin (3) */
     float shape_xf[12];                 /* local transform of the single shape */
@@ -186,6 +189,37 @@ int bpc_body_read_contacts(bpc_context *ctx, int slot, int max_records, bpc_cont
  * records start in `records`), records[bpc_contacts_capacity()]. */
 int bpc_contacts_capacity(bpc_context *ctx);
 int bpc_contacts_read(bpc_context *ctx, int32_t *counts, int32_t *offsets, bpc_contact *records);
+
+/* ---- areas: PhysicsServer3D::area_* (servers/physics_server_3d.h:296-358; P3D/bradot_area_3d.{h,cpp},
+ * P3D/bradot_area_pair_3d.cpp:36-118, the area loop of integrate_forces P3D/bradot_body_3d.cpp:498-585).  An area is a shape
+ * in a space that bodies overlap: one with a space override changes the gravity / damping of the bodies standing in it
+ * (by priority, with the reference's combine / replace rules), one with a monitor callback is told who enters and leaves.
+ * flags: bit0 monitorable, bit1 a body monitor callback is set (events are raised), bit2 the gravity vector is a point
+ * (in the area's space) bodies are pulled towards, bit3 reserved (area monitor callback).  Override modes are
+ * PhysicsServer3D::AreaSpaceOverrideMode: 0 disabled, 1 combine, 2 combine-replace, 3 replace, 4 replace-combine.
+ * Not built: area-against-area monitoring (BradotArea2Pair3D), wind (soft bodies only). */
+typedef struct bpc_area_desc {
+    int32_t space, shape;
+    uint32_t flags;
+    int32_t priority;
+    float xf[12], shape_xf[12];
+    uint32_t layer, mask;
+    int32_t gravity_mode, linear_damp_mode, angular_damp_mode;
+    float gravity, gravity_vector[3], point_unit_distance, linear_damp, angular_damp;
+    uint32_t reserved;
+} bpc_area_desc;
+typedef struct bpc_area_event {
+    int32_t area, body, status; /* status: 0 = AREA_BODY_ADDED, 1 = AREA_BODY_REMOVED */
+} bpc_area_event;
+int bpc_areas_create(bpc_context *ctx, const bpc_area_desc *descs, int n);              /* -> index of the first */
+int bpc_areas_write(bpc_context *ctx, int first, int n, const bpc_area_desc *descs);    /* any area_set_*: also "the area moved" */
+int bpc_areas_destroy(bpc_context *ctx, const int32_t *areas, int n);
+int bpc_area_count(bpc_context *ctx);
+/* Enter / exit events raised since the last call (BradotArea3D::call_queries hands them to the monitor callback); returns how
+ * many there were, writes at most max_events (the rest stay for the next call). */
+int bpc_area_events_read(bpc_context *ctx, bpc_area_event *out, int max_events);
+/* The areas a body stands in right now (bit 30 set: attached as a space override).  At most 8 are tracked per body. */
+int bpc_body_read_areas(bpc_context *ctx, int slot, int32_t *out, int max_areas);
 
 /* Size every per-body and per-pair buffer for `bodies` bodies and `pairs` broadphase pairs up front, so that bpc_step does
  * not allocate while the counts stay below them (a pair burst beyond `pairs` still grows the buffers, once). */

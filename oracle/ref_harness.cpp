@@ -72,7 +72,8 @@ struct ScnHeader {
 	float dt;
 	uint32_t iterations;
 	uint32_t iter_step; // space s sweeps iterations + s * iter_step times
-	uint32_t reserved[6];
+	uint32_t n_areas; // area records after the vertices
+	uint32_t reserved[5];
 };
 struct ScnShape {
 	uint32_t type; // PhysicsServer3D::ShapeType
@@ -102,10 +103,30 @@ struct ScnJoint {
 	uint32_t pad[3];
 };
 struct Event {
-	int32_t step, body, kind;
+	int32_t step, body, kind; // kinds 6 / 7 address an AREA: 6 area_set_transform, 7 free
 	float v[12];
 };
+struct ScnArea { // = bpc_area_desc
+	int32_t space, shape;
+	uint32_t flags; // bit0 monitorable, bit1 body monitor callback, bit2 gravity is a point
+	int32_t priority;
+	float xf[12], shape_xf[12];
+	uint32_t layer, mask;
+	int32_t gravity_mode, linear_damp_mode, angular_damp_mode;
+	float gravity, gravity_vector[3], point_unit_distance, linear_damp, angular_damp;
+	uint32_t reserved;
+};
 #pragma pack(pop)
+
+// what the areas' monitor callbacks were told since the last dump: (area, body, status)
+static std::vector<int32_t> g_area_events;
+static std::map<uint64_t, int> g_body_of_rid;
+static void on_area_monitor(int p_status, const RID &p_body, ObjectID p_instance, int p_body_shape, int p_area_shape, int p_area) {
+	auto it = g_body_of_rid.find(p_body.get_id());
+	g_area_events.push_back(p_area);
+	g_area_events.push_back(it == g_body_of_rid.end() ? -1 : it->second);
+	g_area_events.push_back(p_status);
+}
 
 static Transform3D xf_from(const float *f) {
 	Transform3D t;
@@ -148,7 +169,8 @@ static void put3(std::vector<float> &v, const Vector3 &p) {
 
 struct World {
 	BradotPhysicsServer3D *ps = nullptr;
-	std::vector<RID> spaces, shapes, bodies, joints;
+	std::vector<RID> spaces, shapes, bodies, joints, areas;
+	std::vector<char> area_freed;
 	std::vector<BradotBody3D *> body_ptr;
 	std::map<const BradotBody3D *, int> body_index;
 	std::vector<uint32_t> body_space;
@@ -760,6 +782,8 @@ int main(int argc, char **argv) {
 	if (hd.n_bodies && fread(sbodies.data(), sizeof(ScnBody), hd.n_bodies, sf) != hd.n_bodies) return 2;
 	if (hd.n_joints && fread(sjoints.data(), sizeof(ScnJoint), hd.n_joints, sf) != hd.n_joints) return 2;
 	if (hd.n_verts && fread(sverts.data(), 12, hd.n_verts, sf) != hd.n_verts) return 2;
+	std::vector<ScnArea> sareas(hd.n_areas);
+	if (hd.n_areas && fread(sareas.data(), sizeof(ScnArea), hd.n_areas, sf) != hd.n_areas) return 2;
 	fclose(sf);
 
 	// ---- minimal engine bring-up (order follows Main::test_setup, main/main.cpp:705-747)
@@ -913,6 +937,36 @@ int main(int argc, char **argv) {
 		w.joints.push_back(jr);
 	}
 
+	// areas (servers/physics_server_3d.h:296-358)
+	for (size_t i = 0; i < w.bodies.size(); i++) {
+		g_body_of_rid[w.bodies[i].get_id()] = (int)i;
+	}
+	for (uint32_t i = 0; i < hd.n_areas; i++) {
+		const ScnArea &a = sareas[i];
+		RID ar = ps->area_create();
+		ps->area_add_shape(ar, w.shapes[a.shape], xf_from(a.shape_xf));
+		ps->area_set_transform(ar, xf_from(a.xf));
+		ps->area_set_collision_layer(ar, a.layer);
+		ps->area_set_collision_mask(ar, a.mask);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY_OVERRIDE_MODE, a.gravity_mode);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_LINEAR_DAMP_OVERRIDE_MODE, a.linear_damp_mode);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_ANGULAR_DAMP_OVERRIDE_MODE, a.angular_damp_mode);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY, a.gravity);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY_VECTOR, Vector3(a.gravity_vector[0], a.gravity_vector[1], a.gravity_vector[2]));
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY_IS_POINT, (a.flags & 4) != 0);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY_POINT_UNIT_DISTANCE, a.point_unit_distance);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_LINEAR_DAMP, a.linear_damp);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_ANGULAR_DAMP, a.angular_damp);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_PRIORITY, a.priority);
+		ps->area_set_monitorable(ar, (a.flags & 1) != 0);
+		if (a.flags & 2) {
+			ps->area_set_monitor_callback(ar, callable_mp_static(&on_area_monitor).bind((int)i));
+		}
+		ps->area_set_space(ar, w.spaces[a.space]);
+		w.areas.push_back(ar);
+		w.area_freed.push_back(0);
+	}
+
 	// a state handed over by the other side: transforms and velocities of the moving bodies
 	if (state_path) {
 		FILE *stf = fopen(state_path, "rb");
@@ -979,6 +1033,17 @@ int main(int argc, char **argv) {
 	auto t0 = std::chrono::steady_clock::now();
 	for (int s = 1; s <= steps; s++) {
 		for (const Event &e : events) {
+			if (e.step == s && (e.kind == 6 || e.kind == 7)) {
+				if (e.body >= 0 && e.body < (int)w.areas.size() && !w.area_freed[e.body]) {
+					if (e.kind == 6) {
+						ps->area_set_transform(w.areas[e.body], xf_from(e.v));
+					} else {
+						ps->free(w.areas[e.body]);
+						w.area_freed[e.body] = 1;
+					}
+				}
+				continue;
+			}
 			if (e.step != s || e.body < 0 || e.body >= (int)w.bodies.size() || w.body_freed[e.body]) {
 				continue;
 			}
@@ -1014,6 +1079,15 @@ int main(int argc, char **argv) {
 			for (int k = 0; k < 5; k++) {
 				phase_us[k] += space->get_elapsed_time((BradotSpace3D::ElapsedTime)k);
 			}
+		}
+		if (!w.areas.empty()) {
+			ps->flush_queries(); // the areas' monitor callbacks (BradotSpace3D::call_queries, bradot_space_3d.cpp:1164-1176)
+			if (d.f) { // every step that had events, whether it is a dump step or not
+				if (!g_area_events.empty()) {
+					d.arr("area_events", s, "i4", { (uint64_t)g_area_events.size() / 3, 3 }, g_area_events.data(), g_area_events.size() * 4);
+				}
+			}
+			g_area_events.clear();
 		}
 		if (d.f && dump_this) {
 			dump_step(d, w, s);

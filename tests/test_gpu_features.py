@@ -333,3 +333,56 @@ def test_contact_reporting_matches_the_reference():
     theirs, mine = ref[ref[:, 0] == 1], ps.body_contacts(1, 16)
     assert len(mine) == len(theirs) > 0 and np.array_equal(np.sort(mine["collider"]), np.sort(theirs[:, 14].astype(np.int32)))
     ps.finish()
+
+
+def _apply_area_events(ps, sc, areas, events, step, gone_bodies, gone_areas):
+    for (s, idx, kind, v) in events:
+        if s != step:
+            continue
+        if kind == 6 and idx not in gone_areas:
+            areas[idx]["xf"] = v[:12]
+            ps.areas_write(idx, areas[idx:idx + 1])
+        elif kind == 7 and idx not in gone_areas:
+            ps.areas_destroy([idx])
+            gone_areas.add(idx)
+    _apply_events(ps, [e for e in events if e[2] not in (6, 7)], step, gone_bodies)
+
+
+def test_areas_overrides_and_monitoring_follow_the_reference():
+    """Areas (bradot_area_pair_3d.cpp:36-118, the area loop of integrate_forces bradot_body_3d.cpp:498-585,
+    compute_gravity bradot_area_3d.cpp:312-332, call_queries :232-310): scenes.area_zones() free-running beside the reference
+    running the same script.  No body ever touches another, so the two runs differ by rounding only: after EVERY step the
+    enter / exit events told to the monitor callbacks are the same set, and positions and velocities agree to 1e-4."""
+    _need_oracle()
+    sc = scenes.area_zones()
+    events = scenes.area_zones_script()
+    steps = 130
+    _, dump = parity.run_oracle(sc, steps, events=events, dump_from=0, dump_every=1)
+    ps = parity.new_server(sc)
+    areas = sc.areas.copy()
+    kin = np.nonzero(sc.bodies["mode"] == scenes.MODE_KINEMATIC)[0]
+    gone_b, gone_a = set(), set()
+    seen = {0: 0, 1: 0}
+    for k in range(1, steps + 1):
+        _apply_area_events(ps, sc, areas, events, k, gone_b, gone_a)
+        for row in dump.get(("kin_targets", k), ()):
+            ps.bodies_write(server.FIELD_KINEMATIC_TARGET, row[1:13].reshape(1, 12), first=int(row[0]))
+        ps.step(sc.dt)
+        mine = {tuple(int(x) for x in e) for e in ps.area_events()}
+        ref = {tuple(int(x) for x in e) for e in dump.get(("area_events", k), np.zeros((0, 3), np.int32))}
+        assert mine == ref, (k, sorted(mine - ref), sorted(ref - mine))
+        for e in mine:
+            seen[e[2]] += 1
+        st = ps.bodies_read_state()
+        refb = dump[("bodies", k)]
+        alive = np.array([i not in gone_b for i in range(len(sc.bodies))])
+        assert np.max(np.abs(st[alive, 0:18] - refb[alive, 0:18])) < 1e-4, (k, int(np.argmax(np.abs(st[alive, 0:18] - refb[alive, 0:18]).max(axis=1))))
+        assert np.array_equal(st[alive, 18] != 0, refb[alive, 18] != 0), k
+        if k == 45:      # the zone was moved onto the sleeping box at step 40: attached to it, and the box sleeps on
+            inside, attached = ps.body_areas(13)
+            assert list(inside) == [9] and attached.all() and st[13, 18] == 0
+    assert seen[0] >= 10 and seen[1] >= 8, seen
+    # what the override did: the ball in the well was pulled off its vertical line, the box under the moved zone rose once woken
+    st = ps.bodies_read_state()
+    assert abs(st[5, 9] - 10.0) > 0.05 and st[13, 10] > 3.05
+    ps.finish()
