@@ -483,6 +483,12 @@ void BradotPhysicsServerCUDA::_body_leave_space(Body *p_body) {
 			}
 		}
 		ERR_FAIL_COND_MSG(bpc_bodies_destroy(ctx, &slot, 1) < 0, bpc_last_error(ctx));
+		if (area_owner.get_rid_count() > 0) { // an area it stood in may still have to be told who left
+			FreedBody fb;
+			fb.rid = p_body->self;
+			fb.instance_id = p_body->instance_id;
+			freed_bodies[slot] = fb;
+		}
 		body_of_slot[slot] = nullptr;
 		p_body->slot = -1;
 		state_cache_valid = false;
@@ -1487,6 +1493,394 @@ bool BradotPhysicsServerCUDA::hinge_joint_get_flag(RID p_joint, HingeJointFlag p
 
 // free(RID) of any kind (bradot_physics_server_3d.cpp:1557-1622).  A body leaves the GPU side with its slot (reused by the
 // next upload); freeing a space frees what is in it.
+
+// ---------------------------------------------------------------------------------------------- areas
+// PhysicsServer3D::area_* (servers/physics_server_3d.h:335-381; reference P3D/bradot_physics_server_3d.cpp:215-436).  An area is
+// a host record like a body; it goes to the backend once it has a space and a shape (bpc_areas_create), every later setter
+// marks it and the whole record is written again before the next step (bpc_areas_write, which also counts as "the area moved").
+// A space RID in place of an area RID addresses the space's default area, as in the reference (:291-295).
+RID BradotPhysicsServerCUDA::area_create() {
+	Area *area = memnew(Area);
+	RID rid = area_owner.make_rid(area);
+	area->self = rid;
+	return rid;
+}
+
+void BradotPhysicsServerCUDA::_fill_area_desc(const Area *p_area, bpc_area_desc &r_desc) {
+	memset(&r_desc, 0, sizeof(r_desc));
+	const Space *space = space_owner.get_or_null(p_area->space);
+	Shape *shape = shape_owner.get_or_null(p_area->shape);
+	r_desc.space = space ? space->handle : -1;
+	r_desc.shape = shape ? _shape_handle(shape) : -1;
+	r_desc.flags = (p_area->monitorable ? 1u : 0u) | (p_area->monitor_callback.is_valid() ? 2u : 0u) | (p_area->gravity_is_point ? 4u : 0u);
+	r_desc.priority = p_area->priority;
+	_xf_to_floats(p_area->xf, r_desc.xf);
+	_xf_to_floats(p_area->shape_xf, r_desc.shape_xf);
+	r_desc.layer = p_area->layer;
+	r_desc.mask = p_area->mask;
+	r_desc.gravity_mode = p_area->gravity_mode;
+	r_desc.linear_damp_mode = p_area->linear_damp_mode;
+	r_desc.angular_damp_mode = p_area->angular_damp_mode;
+	r_desc.gravity = p_area->gravity;
+	r_desc.gravity_vector[0] = p_area->gravity_vector.x;
+	r_desc.gravity_vector[1] = p_area->gravity_vector.y;
+	r_desc.gravity_vector[2] = p_area->gravity_vector.z;
+	r_desc.point_unit_distance = p_area->point_unit_distance;
+	r_desc.linear_damp = p_area->linear_damp;
+	r_desc.angular_damp = p_area->angular_damp;
+}
+
+// a setter touched the area: upload it if it can be now, else write it again before the next step
+void BradotPhysicsServerCUDA::_area_changed(Area *p_area) {
+	const bool wanted = p_area->space.is_valid() && p_area->shape.is_valid() && !p_area->shape_disabled;
+	if (p_area->handle >= 0) {
+		if (!wanted) {
+			_area_leave_space(p_area);
+		} else if (!p_area->dirty) {
+			p_area->dirty = true;
+			dirty_areas.push_back(p_area);
+		}
+	} else if (wanted && !p_area->pending) {
+		p_area->pending = true;
+		pending_areas.push_back(p_area);
+	}
+}
+
+void BradotPhysicsServerCUDA::_area_leave_space(Area *p_area) {
+	if (p_area->pending) {
+		pending_areas.erase(p_area);
+		p_area->pending = false;
+	}
+	if (p_area->dirty) {
+		dirty_areas.erase(p_area);
+		p_area->dirty = false;
+	}
+	if (p_area->handle >= 0) {
+		int32_t h = p_area->handle;
+		ERR_FAIL_COND_MSG(bpc_areas_destroy(ctx, &h, 1) < 0, bpc_last_error(ctx));
+		area_of_handle[h] = nullptr;
+		p_area->handle = -1;
+	}
+}
+
+void BradotPhysicsServerCUDA::area_set_space(RID p_area, RID p_space) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	if (p_space.is_valid()) {
+		ERR_FAIL_NULL(space_owner.get_or_null(p_space));
+	}
+	if (area->space == p_space) {
+		return;
+	}
+	_area_leave_space(area); // an area does not change space on the backend: it leaves and is created anew
+	area->space = p_space;
+	_area_changed(area);
+}
+
+RID BradotPhysicsServerCUDA::area_get_space(RID p_area) const {
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, RID());
+	return area->space;
+}
+
+void BradotPhysicsServerCUDA::area_add_shape(RID p_area, RID p_shape, const Transform3D &p_transform, bool p_disabled) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
+	ERR_FAIL_COND_MSG(area->shape.is_valid(), "BradotPhysicsCUDA: an area has one shape (several shapes per object are not built).");
+	area->shape = p_shape;
+	area->shape_xf = p_transform;
+	area->shape_disabled = p_disabled;
+	_area_changed(area);
+}
+
+void BradotPhysicsServerCUDA::area_set_shape(RID p_area, int p_shape_idx, RID p_shape) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	ERR_FAIL_COND(p_shape_idx != 0 || !area->shape.is_valid());
+	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
+	area->shape = p_shape;
+	_area_changed(area);
+}
+
+void BradotPhysicsServerCUDA::area_set_shape_transform(RID p_area, int p_shape_idx, const Transform3D &p_transform) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	ERR_FAIL_COND(p_shape_idx != 0 || !area->shape.is_valid());
+	area->shape_xf = p_transform;
+	_area_changed(area);
+}
+
+int BradotPhysicsServerCUDA::area_get_shape_count(RID p_area) const {
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, -1);
+	return area->shape.is_valid() ? 1 : 0;
+}
+
+RID BradotPhysicsServerCUDA::area_get_shape(RID p_area, int p_shape_idx) const {
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, RID());
+	ERR_FAIL_COND_V(p_shape_idx != 0, RID());
+	return area->shape;
+}
+
+Transform3D BradotPhysicsServerCUDA::area_get_shape_transform(RID p_area, int p_shape_idx) const {
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, Transform3D());
+	ERR_FAIL_COND_V(p_shape_idx != 0, Transform3D());
+	return area->shape_xf;
+}
+
+void BradotPhysicsServerCUDA::area_remove_shape(RID p_area, int p_shape_idx) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	ERR_FAIL_COND(p_shape_idx != 0 || !area->shape.is_valid());
+	area->shape = RID();
+	_area_changed(area);
+}
+
+void BradotPhysicsServerCUDA::area_clear_shapes(RID p_area) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	area->shape = RID();
+	_area_changed(area);
+}
+
+void BradotPhysicsServerCUDA::area_set_shape_disabled(RID p_area, int p_shape_idx, bool p_disabled) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	ERR_FAIL_COND(p_shape_idx != 0 || !area->shape.is_valid());
+	area->shape_disabled = p_disabled;
+	_area_changed(area);
+}
+
+void BradotPhysicsServerCUDA::area_attach_object_instance_id(RID p_area, ObjectID p_id) {
+	if (space_owner.owns(p_area)) {
+		return; // the default area of a space is nobody's node
+	}
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	area->instance_id = p_id;
+}
+
+ObjectID BradotPhysicsServerCUDA::area_get_object_instance_id(RID p_area) const {
+	if (space_owner.owns(p_area)) {
+		return ObjectID();
+	}
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, ObjectID());
+	return area->instance_id;
+}
+
+
+void BradotPhysicsServerCUDA::area_set_param(RID p_area, AreaParameter p_param, const Variant &p_value) {
+	if (space_owner.owns(p_area)) { // the default area: what bodies get where no area settles gravity / damping
+		Space *space = space_owner.get_or_null(p_area);
+		switch (p_param) {
+			case AREA_PARAM_GRAVITY: space->default_gravity = p_value; break;
+			case AREA_PARAM_GRAVITY_VECTOR: space->default_gravity_vector = p_value; break;
+			case AREA_PARAM_LINEAR_DAMP: space->default_linear_damp = p_value; break;
+			case AREA_PARAM_ANGULAR_DAMP: space->default_angular_damp = p_value; break;
+			default: return; // override modes, point gravity, priority and wind mean nothing on the default area of this backend
+		}
+		// compute_gravity of a non-point area: vector * magnitude in fp32 (P3D/bradot_area_3d.cpp:330)
+		Vector3 g = space->default_gravity_vector * space->default_gravity;
+		bpc_space_set_param(ctx, space->handle, BPC_SPACE_GRAVITY_X, g.x);
+		bpc_space_set_param(ctx, space->handle, BPC_SPACE_GRAVITY_Y, g.y);
+		bpc_space_set_param(ctx, space->handle, BPC_SPACE_GRAVITY_Z, g.z);
+		bpc_space_set_param(ctx, space->handle, BPC_SPACE_LINEAR_DAMP, space->default_linear_damp);
+		bpc_space_set_param(ctx, space->handle, BPC_SPACE_ANGULAR_DAMP, space->default_angular_damp);
+		return;
+	}
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	switch (p_param) {
+		case AREA_PARAM_GRAVITY_OVERRIDE_MODE: area->gravity_mode = p_value; break;
+		case AREA_PARAM_GRAVITY: area->gravity = p_value; break;
+		case AREA_PARAM_GRAVITY_VECTOR: area->gravity_vector = p_value; break;
+		case AREA_PARAM_GRAVITY_IS_POINT: area->gravity_is_point = p_value; break;
+		case AREA_PARAM_GRAVITY_POINT_UNIT_DISTANCE: area->point_unit_distance = p_value; break;
+		case AREA_PARAM_LINEAR_DAMP_OVERRIDE_MODE: area->linear_damp_mode = p_value; break;
+		case AREA_PARAM_LINEAR_DAMP: area->linear_damp = p_value; break;
+		case AREA_PARAM_ANGULAR_DAMP_OVERRIDE_MODE: area->angular_damp_mode = p_value; break;
+		case AREA_PARAM_ANGULAR_DAMP: area->angular_damp = p_value; break;
+		case AREA_PARAM_PRIORITY: area->priority = p_value; break;
+		case AREA_PARAM_WIND_FORCE_MAGNITUDE: area->wind[0] = p_value; return;
+		case AREA_PARAM_WIND_SOURCE: area->wind[1] = p_value; return;
+		case AREA_PARAM_WIND_DIRECTION: area->wind[2] = p_value; return;
+		case AREA_PARAM_WIND_ATTENUATION_FACTOR: area->wind[3] = p_value; return;
+	}
+	_area_changed(area);
+}
+
+Variant BradotPhysicsServerCUDA::area_get_param(RID p_area, AreaParameter p_param) const {
+	if (space_owner.owns(p_area)) {
+		const Space *space = space_owner.get_or_null(p_area);
+		switch (p_param) {
+			case AREA_PARAM_GRAVITY: return space->default_gravity;
+			case AREA_PARAM_GRAVITY_VECTOR: return space->default_gravity_vector;
+			case AREA_PARAM_LINEAR_DAMP: return space->default_linear_damp;
+			case AREA_PARAM_ANGULAR_DAMP: return space->default_angular_damp;
+			case AREA_PARAM_GRAVITY_IS_POINT: return false;
+			default: return 0;
+		}
+	}
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, Variant());
+	switch (p_param) {
+		case AREA_PARAM_GRAVITY_OVERRIDE_MODE: return area->gravity_mode;
+		case AREA_PARAM_GRAVITY: return area->gravity;
+		case AREA_PARAM_GRAVITY_VECTOR: return area->gravity_vector;
+		case AREA_PARAM_GRAVITY_IS_POINT: return area->gravity_is_point;
+		case AREA_PARAM_GRAVITY_POINT_UNIT_DISTANCE: return area->point_unit_distance;
+		case AREA_PARAM_LINEAR_DAMP_OVERRIDE_MODE: return area->linear_damp_mode;
+		case AREA_PARAM_LINEAR_DAMP: return area->linear_damp;
+		case AREA_PARAM_ANGULAR_DAMP_OVERRIDE_MODE: return area->angular_damp_mode;
+		case AREA_PARAM_ANGULAR_DAMP: return area->angular_damp;
+		case AREA_PARAM_PRIORITY: return area->priority;
+		case AREA_PARAM_WIND_FORCE_MAGNITUDE: return area->wind[0];
+		case AREA_PARAM_WIND_SOURCE: return area->wind[1];
+		case AREA_PARAM_WIND_DIRECTION: return area->wind[2];
+		case AREA_PARAM_WIND_ATTENUATION_FACTOR: return area->wind[3];
+	}
+	return Variant();
+}
+
+void BradotPhysicsServerCUDA::area_set_transform(RID p_area, const Transform3D &p_transform) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	area->xf = p_transform;
+	_area_changed(area);
+}
+
+Transform3D BradotPhysicsServerCUDA::area_get_transform(RID p_area) const {
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, Transform3D());
+	return area->xf;
+}
+
+void BradotPhysicsServerCUDA::area_set_collision_layer(RID p_area, uint32_t p_layer) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	area->layer = p_layer;
+	_area_changed(area);
+}
+
+uint32_t BradotPhysicsServerCUDA::area_get_collision_layer(RID p_area) const {
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, 0);
+	return area->layer;
+}
+
+void BradotPhysicsServerCUDA::area_set_collision_mask(RID p_area, uint32_t p_mask) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	area->mask = p_mask;
+	_area_changed(area);
+}
+
+uint32_t BradotPhysicsServerCUDA::area_get_collision_mask(RID p_area) const {
+	const Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL_V(area, 0);
+	return area->mask;
+}
+
+void BradotPhysicsServerCUDA::area_set_monitorable(RID p_area, bool p_monitorable) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	if (area->monitorable == p_monitorable) {
+		return;
+	}
+	area->monitorable = p_monitorable;
+	_area_changed(area);
+}
+
+void BradotPhysicsServerCUDA::area_set_monitor_callback(RID p_area, const Callable &p_callback) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	area->monitor_callback = p_callback.is_valid() ? p_callback : Callable();
+	_area_changed(area);
+}
+
+void BradotPhysicsServerCUDA::area_set_area_monitor_callback(RID p_area, const Callable &p_callback) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	area->area_monitor_callback = p_callback.is_valid() ? p_callback : Callable();
+	if (p_callback.is_valid()) {
+		WARN_PRINT_ONCE("BradotPhysicsCUDA: areas do not monitor other areas yet (BradotArea2Pair3D is not built); the callback is kept and never called.");
+	}
+}
+
+void BradotPhysicsServerCUDA::area_set_ray_pickable(RID p_area, bool p_enable) {
+	Area *area = area_owner.get_or_null(p_area);
+	ERR_FAIL_NULL(area);
+	area->ray_pickable = p_enable;
+}
+
+// BradotArea3D::call_queries (P3D/bradot_area_3d.cpp:232-271): what happened to each (area, body) since the last flush, summed
+// (entered and left again = nothing), handed to the area's monitor callback as (status, body RID, object id, body shape, area shape)
+void BradotPhysicsServerCUDA::_flush_area_events() {
+	if (area_owner.get_rid_count() == 0 && freed_bodies.is_empty()) {
+		return;
+	}
+	LocalVector<bpc_area_event> ev;
+	ev.resize(4096);
+	int n = bpc_area_events_read(ctx, ev.ptr(), (int)ev.size());
+	if (n > (int)ev.size()) { // more than fitted: the rest waited in the backend
+		uint32_t had = ev.size();
+		ev.resize(n);
+		int more = bpc_area_events_read(ctx, ev.ptr() + had, n - (int)had);
+		n = (int)had + MAX(more, 0);
+	}
+	if (n <= 0) {
+		freed_bodies.clear();
+		return;
+	}
+	HashMap<uint64_t, int> state; // (area << 32 | body) -> entered minus left
+	LocalVector<uint64_t> order;
+	for (int i = 0; i < n && i < (int)ev.size(); i++) {
+		uint64_t key = ((uint64_t)(uint32_t)ev[i].area << 32) | (uint32_t)ev[i].body;
+		if (!state.has(key)) {
+			state[key] = 0;
+			order.push_back(key);
+		}
+		state[key] += ev[i].status == 0 ? 1 : -1;
+	}
+	for (uint64_t key : order) {
+		int s = state[key];
+		if (s == 0) {
+			continue;
+		}
+		uint32_t ai = (uint32_t)(key >> 32);
+		int32_t slot = (int32_t)(uint32_t)key;
+		Area *area = ai < area_of_handle.size() ? area_of_handle[ai] : nullptr;
+		if (!area || !area->monitor_callback.is_valid()) {
+			continue;
+		}
+		RID body_rid;
+		ObjectID body_id;
+		Body *b = (slot >= 0 && (uint32_t)slot < body_of_slot.size()) ? body_of_slot[slot] : nullptr;
+		if (freed_bodies.has(slot) && s < 0) { // it left by being freed: the event still names it
+			body_rid = freed_bodies[slot].rid;
+			body_id = freed_bodies[slot].instance_id;
+		} else if (b) {
+			body_rid = b->self;
+			body_id = b->instance_id;
+		} else {
+			continue;
+		}
+		Variant res[5] = { s > 0 ? AREA_BODY_ADDED : AREA_BODY_REMOVED, body_rid, body_id, 0, 0 };
+		const Variant *resptr[5] = { &res[0], &res[1], &res[2], &res[3], &res[4] };
+		Callable::CallError ce;
+		Variant ret;
+		area->monitor_callback.callp(resptr, 5, ret, ce);
+		if (ce.error != Callable::CallError::CALL_OK) {
+			ERR_PRINT_ONCE("Error calling monitor callback method " + Variant::get_callable_error_text(area->monitor_callback, resptr, 5, ce));
+		}
+	}
+	freed_bodies.clear();
+}
+
 void BradotPhysicsServerCUDA::free(RID p_rid) {
 	if (shape_owner.owns(p_rid)) {
 		Shape *s = shape_owner.get_or_null(p_rid);
@@ -1527,6 +1921,15 @@ void BradotPhysicsServerCUDA::free(RID p_rid) {
 				b->space = RID();
 			}
 		}
+		List<RID> areas;
+		area_owner.get_owned_list(&areas);
+		for (const RID &ar : areas) {
+			Area *a = area_owner.get_or_null(ar);
+			if (a && a->space == p_rid) {
+				_area_leave_space(a);
+				a->space = RID();
+			}
+		}
 		bpc_space_destroy(ctx, s->handle);
 		if (s->direct_state) {
 			memdelete(s->direct_state);
@@ -1538,6 +1941,11 @@ void BradotPhysicsServerCUDA::free(RID p_rid) {
 		joint_clear(p_rid);
 		joint_owner.free(p_rid);
 		memdelete(j);
+	} else if (area_owner.owns(p_rid)) {
+		Area *a = area_owner.get_or_null(p_rid);
+		_area_leave_space(a);
+		area_owner.free(p_rid);
+		memdelete(a);
 	} else {
 		ERR_FAIL_MSG("Invalid ID.");
 	}
@@ -1660,6 +2068,37 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 			}
 		}
 	}
+	LocalVector<Area *> waiting_areas;
+	for (Area *a : pending_areas) {
+		bpc_area_desc d;
+		_fill_area_desc(a, d);
+		if (d.space < 0 || d.shape < 0) {
+			waiting_areas.push_back(a); // its shape has no data yet
+			continue;
+		}
+		a->pending = false;
+		int h = bpc_areas_create(ctx, &d, 1);
+		ERR_CONTINUE_MSG(h < 0, bpc_last_error(ctx));
+		a->handle = h;
+		if (area_of_handle.size() <= (uint32_t)h) {
+			area_of_handle.resize(h + 1);
+		}
+		area_of_handle[h] = a;
+	}
+	pending_areas.clear();
+	for (Area *a : waiting_areas) {
+		pending_areas.push_back(a);
+	}
+	for (Area *a : dirty_areas) {
+		a->dirty = false;
+		if (a->handle < 0) {
+			continue;
+		}
+		bpc_area_desc d;
+		_fill_area_desc(a, d);
+		ERR_CONTINUE_MSG(bpc_areas_write(ctx, a->handle, 1, &d) < 0, bpc_last_error(ctx));
+	}
+	dirty_areas.clear();
 }
 
 void BradotPhysicsServerCUDA::step(real_t p_step) {
@@ -1748,6 +2187,7 @@ void BradotPhysicsServerCUDA::flush_queries() {
 			}
 		}
 	}
+	_flush_area_events(); // after the bodies, as BradotSpace3D::call_queries does (P3D/bradot_space_3d.cpp:1164-1176)
 	flushing_queries = false;
 }
 

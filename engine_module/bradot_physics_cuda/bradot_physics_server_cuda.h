@@ -13,6 +13,7 @@
 #ifndef BRADOT_PHYSICS_SERVER_CUDA_H
 #define BRADOT_PHYSICS_SERVER_CUDA_H
 
+#include "core/templates/hash_map.h"
 #include "core/templates/local_vector.h"
 #include "core/templates/rid_owner.h"
 #include "servers/physics_server_3d.h"
@@ -116,6 +117,9 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		bool active = false;
 		BradotPhysicsDirectSpaceStateCUDA *direct_state = nullptr;
 		real_t params[8] = { 0.01, 0.05, 0.01, 0.8, 0.1, Math::deg_to_rad(8.0), 0.5, 16 };
+		// the space's default area (P3D/bradot_space_3d.cpp:1220-1226; BradotArea3D defaults)
+		real_t default_gravity = 9.80665, default_linear_damp = 0.1, default_angular_damp = 0.1;
+		Vector3 default_gravity_vector = Vector3(0, -1, 0);
 	};
 	struct Body {
 		RID self, space, shape;
@@ -159,7 +163,35 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		int handle = -1;
 	};
 
+	struct Area { // BradotArea3D (P3D/bradot_area_3d.h:46-70), one shape
+		RID self, space, shape;
+		Transform3D xf, shape_xf;
+		bool shape_disabled = false;
+		uint32_t layer = 1, mask = 1;
+		bool monitorable = false, ray_pickable = false, gravity_is_point = false;
+		Callable monitor_callback, area_monitor_callback;
+		ObjectID instance_id;
+		int gravity_mode = 0, linear_damp_mode = 0, angular_damp_mode = 0, priority = 0;
+		real_t gravity = 9.80665, point_unit_distance = 0.0, linear_damp = 0.1, angular_damp = 0.1;
+		Vector3 gravity_vector = Vector3(0, -1, 0);
+		Variant wind[4]; // stored, used by soft bodies only
+		bool pending = false, dirty = false;
+		int handle = -1; // bpc area index once uploaded
+	};
+	struct FreedBody { // what an exit event of a body freed since the last flush_queries() still has to name
+		RID rid;
+		ObjectID instance_id;
+	};
+
 	mutable RID_PtrOwner<Shape, true> shape_owner;
+	mutable RID_PtrOwner<Area, true> area_owner;
+	LocalVector<Area *> pending_areas, dirty_areas;
+	LocalVector<Area *> area_of_handle;
+	HashMap<int32_t, FreedBody> freed_bodies;
+	void _area_changed(Area *p_area);
+	void _area_leave_space(Area *p_area);
+	void _fill_area_desc(const Area *p_area, bpc_area_desc &r_desc);
+	void _flush_area_events();
 	mutable RID_PtrOwner<Space, true> space_owner;
 	mutable RID_PtrOwner<Body, true> body_owner;
 	mutable RID_PtrOwner<Joint, true> joint_owner;
@@ -234,6 +266,33 @@ public:
 	virtual void space_set_param(RID p_space, SpaceParameter p_param, real_t p_value) override;
 	virtual real_t space_get_param(RID p_space, SpaceParameter p_param) const override;
 	virtual PhysicsDirectSpaceState3D *space_get_direct_state(RID p_space) override;
+	// areas
+	virtual RID area_create() override;
+	virtual void area_set_space(RID p_area, RID p_space) override;
+	virtual RID area_get_space(RID p_area) const override;
+	virtual void area_add_shape(RID p_area, RID p_shape, const Transform3D &p_transform = Transform3D(), bool p_disabled = false) override;
+	virtual void area_set_shape(RID p_area, int p_shape_idx, RID p_shape) override;
+	virtual void area_set_shape_transform(RID p_area, int p_shape_idx, const Transform3D &p_transform) override;
+	virtual int area_get_shape_count(RID p_area) const override;
+	virtual RID area_get_shape(RID p_area, int p_shape_idx) const override;
+	virtual Transform3D area_get_shape_transform(RID p_area, int p_shape_idx) const override;
+	virtual void area_remove_shape(RID p_area, int p_shape_idx) override;
+	virtual void area_clear_shapes(RID p_area) override;
+	virtual void area_set_shape_disabled(RID p_area, int p_shape_idx, bool p_disabled) override;
+	virtual void area_attach_object_instance_id(RID p_area, ObjectID p_id) override;
+	virtual ObjectID area_get_object_instance_id(RID p_area) const override;
+	virtual void area_set_param(RID p_area, AreaParameter p_param, const Variant &p_value) override;
+	virtual void area_set_transform(RID p_area, const Transform3D &p_transform) override;
+	virtual Variant area_get_param(RID p_parea, AreaParameter p_param) const override;
+	virtual Transform3D area_get_transform(RID p_area) const override;
+	virtual void area_set_collision_layer(RID p_area, uint32_t p_layer) override;
+	virtual uint32_t area_get_collision_layer(RID p_area) const override;
+	virtual void area_set_collision_mask(RID p_area, uint32_t p_mask) override;
+	virtual uint32_t area_get_collision_mask(RID p_area) const override;
+	virtual void area_set_monitorable(RID p_area, bool p_monitorable) override;
+	virtual void area_set_monitor_callback(RID p_area, const Callable &p_callback) override;
+	virtual void area_set_area_monitor_callback(RID p_area, const Callable &p_callback) override;
+	virtual void area_set_ray_pickable(RID p_area, bool p_enable) override;
 	// bodies
 	virtual RID body_create() override;
 	virtual void body_set_space(RID p_body, RID p_space) override;

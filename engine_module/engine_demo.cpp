@@ -34,12 +34,34 @@ public:
 };
 
 #pragma pack(push, 1)
-struct ScnHeader { char magic[4]; uint32_t version, n_spaces, n_shapes, n_bodies, n_joints, n_verts; float dt; uint32_t iterations, iter_step, reserved[6]; };
+struct ScnHeader { char magic[4]; uint32_t version, n_spaces, n_shapes, n_bodies, n_joints, n_verts; float dt; uint32_t iterations, iter_step, n_areas, reserved[5]; };
 struct ScnShape { uint32_t type; float p[4]; uint32_t vert_ofs, vert_cnt, pad; };
 struct ScnBody { uint32_t space, mode, shape, flags; float xf[12], shape_xf[12], linvel[3], angvel[3], mass, friction, bounce, gravity_scale, lin_damp, ang_damp; uint32_t layer, mask; };
 struct ScnJoint { uint32_t type, body_a, body_b, flags; float fa[12], fb[12], params[8]; uint32_t priority, pad[3]; };
-struct Event { int32_t step, body, kind; float v[12]; };
+struct Event { int32_t step, body, kind; float v[12]; }; // kinds 6 / 7 address an area: area_set_transform / free
+struct ScnArea { int32_t space, shape; uint32_t flags; int32_t priority; float xf[12], shape_xf[12]; uint32_t layer, mask; int32_t gravity_mode, linear_damp_mode, angular_damp_mode;
+	float gravity, gravity_vector[3], point_unit_distance, linear_damp, angular_damp; uint32_t reserved; };
 #pragma pack(pop)
+
+// what the areas' monitor callbacks were told: (step whose results were flushed, area, body, status)
+static std::vector<int> g_area_events;
+static std::vector<RID> *g_body_rids = nullptr;
+static int g_flushed_step = 0;
+static void on_area_monitor(int p_status, const RID &p_body, ObjectID p_instance, int p_body_shape, int p_area_shape, int p_area) {
+	int idx = -1;
+	for (size_t k = 0; g_body_rids && k < g_body_rids->size(); k++) {
+		if ((*g_body_rids)[k] == p_body) {
+			idx = (int)k;
+		}
+	}
+	if (idx >= 0 && (uint64_t)p_instance != (uint64_t)(1000 + idx)) {
+		idx = -2; // the object id handed over is not the one attached to that body
+	}
+	g_area_events.push_back(g_flushed_step);
+	g_area_events.push_back(p_area);
+	g_area_events.push_back(idx);
+	g_area_events.push_back(p_status);
+}
 
 // what the state-sync callbacks reported: last transform per body, number of calls
 static std::vector<Transform3D> g_synced;
@@ -100,6 +122,8 @@ int main(int argc, char **argv) {
 	if (hd.n_bodies && fread(bodies.data(), sizeof(ScnBody), hd.n_bodies, sf) != hd.n_bodies) return 2;
 	if (hd.n_joints && fread(joints.data(), sizeof(ScnJoint), hd.n_joints, sf) != hd.n_joints) return 2;
 	if (hd.n_verts && fread(verts.data(), 12, hd.n_verts, sf) != hd.n_verts) return 2;
+	std::vector<ScnArea> sareas(hd.n_areas);
+	if (hd.n_areas && fread(sareas.data(), sizeof(ScnArea), hd.n_areas, sf) != hd.n_areas) return 2;
 	fclose(sf);
 
 	OSHeadless os;
@@ -246,11 +270,52 @@ int main(int argc, char **argv) {
 		}
 		joint_r.push_back(jr);
 	}
+	// areas through the RID API, every monitoring one with a callback
+	std::vector<RID> area_r;
+	std::vector<char> area_freed;
+	g_body_rids = &body_r;
+	for (uint32_t i = 0; i < hd.n_areas; i++) {
+		const ScnArea &a = sareas[i];
+		RID ar = ps->area_create();
+		ps->area_add_shape(ar, shape_r[a.shape], xf_from(a.shape_xf));
+		ps->area_set_transform(ar, xf_from(a.xf));
+		ps->area_set_collision_layer(ar, a.layer);
+		ps->area_set_collision_mask(ar, a.mask);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY_OVERRIDE_MODE, a.gravity_mode);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_LINEAR_DAMP_OVERRIDE_MODE, a.linear_damp_mode);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_ANGULAR_DAMP_OVERRIDE_MODE, a.angular_damp_mode);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY, a.gravity);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY_VECTOR, Vector3(a.gravity_vector[0], a.gravity_vector[1], a.gravity_vector[2]));
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY_IS_POINT, (a.flags & 4) != 0);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_GRAVITY_POINT_UNIT_DISTANCE, a.point_unit_distance);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_LINEAR_DAMP, a.linear_damp);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_ANGULAR_DAMP, a.angular_damp);
+		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_PRIORITY, a.priority);
+		ps->area_set_monitorable(ar, (a.flags & 1) != 0);
+		if (a.flags & 2) {
+			ps->area_set_monitor_callback(ar, callable_mp_static(&on_area_monitor).bind((int)i));
+		}
+		ps->area_set_space(ar, space_r[a.space]);
+		area_r.push_back(ar);
+		area_freed.push_back(0);
+	}
 	// the engine's tick (main/main.cpp:4368-4397): sync -> flush_queries (callbacks) -> [user code] -> end_sync -> step
 	for (int s = 1; s <= steps; s++) {
 		ps->sync();
+		g_flushed_step = s - 1;
 		ps->flush_queries();
 		for (const Event &e : events) { // "user code": the script, through the RID API
+			if (e.step == s && (e.kind == 6 || e.kind == 7)) {
+				if (e.body >= 0 && e.body < (int)area_r.size() && !area_freed[e.body]) {
+					if (e.kind == 6) {
+						ps->area_set_transform(area_r[e.body], xf_from(e.v));
+					} else {
+						ps->free(area_r[e.body]);
+						area_freed[e.body] = 1;
+					}
+				}
+				continue;
+			}
 			if (e.step != s || e.body < 0 || e.body >= (int)body_r.size() || freed[e.body]) {
 				continue;
 			}
@@ -272,6 +337,7 @@ int main(int argc, char **argv) {
 		ps->step(hd.dt);
 	}
 	ps->sync();
+	g_flushed_step = steps;
 	ps->flush_queries(); // the callbacks of the last step
 	ps->end_sync();
 	ps->sync();
@@ -334,6 +400,10 @@ int main(int argc, char **argv) {
 	}
 	// cast_motion and rest_info through the RID API: a sphere dropped from above each of the first bodies with that body excluded
 	// (so it lands on whatever lies under it), and the same sphere resting at the body's own place
+	printf("], \"area_events\": [");
+	for (size_t i = 0; i + 3 < g_area_events.size(); i += 4) {
+		printf("%s[%d, %d, %d, %d]", i ? ", " : "", g_area_events[i], g_area_events[i + 1], g_area_events[i + 2], g_area_events[i + 3]);
+	}
 	printf("], \"casts\": [");
 	RID probe = ps->sphere_shape_create();
 	ps->shape_set_data(probe, 0.3f);

@@ -181,3 +181,38 @@ def test_engine_module_reported_contacts_match_direct_c_abi(tmp_path):
         assert np.array_equal(got[o1].astype(np.float32), want[o2].astype(np.float32)), body
         seen += len(mine)
     assert seen > 40
+
+
+def test_engine_module_areas_match_direct_c_abi(tmp_path):
+    """area_* through the RID API (areas created like Area3D nodes do, a monitor callback on every monitoring one, the script
+    moving and freeing areas and freeing a body inside one) against the same scene and script on the C ABI: the callbacks heard
+    the same (step, area, body, status) events, with the right body RID and object id, and the bodies end bit-equal."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    sc = scenes.area_zones()
+    events = scenes.area_zones_script()
+    steps = 100
+    path, evp = str(tmp_path / "scene.bscn"), str(tmp_path / "events.bin")
+    sc.write(path)
+    parity.write_events(evp, events)
+    r = subprocess.run([DEMO, path, str(steps), "--events", evp], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    heard = sorted(tuple(e) for e in out["area_events"])
+    from test_gpu_features import _apply_area_events
+    ps = parity.new_server(sc)
+    areas = sc.areas.copy()
+    gone_b, gone_a = set(), set()
+    mine = []
+    for s in range(1, steps + 1):
+        _apply_area_events(ps, sc, areas, events, s, gone_b, gone_a)
+        ps.step(sc.dt)
+        mine += [(s, int(e[0]), int(e[1]), int(e[2])) for e in ps.area_events()]
+    st = ps.bodies_read_state()
+    ps.finish()
+    mine = sorted(mine)     # (the body freed before step 55 leaves its zone then: both sides hear it with that step's events)
+    assert heard == mine, (sorted(set(heard) - set(mine)), sorted(set(mine) - set(heard)))
+    assert len(heard) > 15 and all(e[2] >= 0 for e in heard)
+    alive = np.array([i not in gone_b for i in range(len(sc.bodies))])
+    engine = np.array(out["origins"], np.float32)
+    assert np.array_equal(engine[alive], st[alive, 9:12]), float(np.abs(engine[alive] - st[alive, 9:12]).max())
