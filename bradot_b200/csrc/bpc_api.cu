@@ -48,7 +48,7 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
     ctx->island.free_(); ctx->island_flag.free_(); ctx->shapes.free_(); ctx->meshes.free_(); ctx->mverts.free_();
     ctx->mplanes.free_(); ctx->medges.free_(); ctx->mfaces.free_(); ctx->mindex.free_(); ctx->d_spaces.free_();
     ctx->d_areas.free_(); ctx->area_list.free_(); ctx->area_start.free_(); ctx->body_area_cnt.free_(); ctx->body_area.free_(); ctx->area_events.free_();
-    ctx->q_exclude.free_();
+    ctx->q_exclude.free_(); ctx->aa_pairs.free_(); ctx->aa_result.free_();
     ctx->keys.free_(); ctx->keys_alt.free_(); ctx->vals.free_(); ctx->vals_alt.free_(); ctx->hist.free_();
     ctx->leaf_min.free_(); ctx->leaf_max.free_(); ctx->nodes.free_(); ctx->node_parent.free_(); ctx->node_flag.free_(); ctx->node_maxleaf.free_();
     ctx->big_items.free_(); ctx->big_start.free_(); ctx->bounds.free_(); ctx->counters.free_(); ctx->pair_keys_raw.free_();

@@ -329,6 +329,13 @@ struct bpc_context {
     std::vector<uint32_t> area_reset_slots;   // body slots reused since the last step: their area lists start empty
     uint32_t body_area_cap = 0;               // bodies the per-body arrays are sized for
     bool areas_dirty = false, areas_moved = false;
+    // area against area (BradotArea2Pair3D): candidates of the coming / last step, their overlap bytes, who overlaps whom
+    struct AreaPairCand { uint32_t a, b, flags_a, flags_b, layer_a, mask_a, layer_b, mask_b; };
+    std::vector<AreaPairCand> aa_cand;
+    DevBuf<uint2> aa_pairs;
+    DevBuf<uint32_t> aa_result;
+    bool aa_launched = false;
+    std::vector<uint64_t> aa_colliding; // sorted (a << 32 | b): a's mask meets b's layer and the shapes overlap
     uint32_t n_areas_alive = 0;
     bool report_dirty = false;
 

@@ -124,6 +124,18 @@ __global__ void __launch_bounds__(128) k_area_pairs(ArArgs a) {
     a.body_area_cnt[i] = cnt;
 }
 
+// BradotArea2Pair3D::setup, the shape half: do areas a and b overlap?  (layers, callbacks and the bookkeeping are the host's:
+// a handful of pairs, looked at only in steps where an area moved)
+__global__ void __launch_bounds__(64) k_area_area(ArArgs a, uint32_t n, const uint2 *__restrict__ pairs, uint32_t *__restrict__ result) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const AreaRec ra = a.areas[pairs[t].x], rb = a.areas[pairs[t].y];
+    Sh sa = ar_shape(a, ra.shape_type, ra.shape_p), sb = ar_shape(a, rb.shape_type, rb.shape_p);
+    X3 xa(M3(f4v(ra.s0), f4v(ra.s1), f4v(ra.s2)), f4v(ra.so)), xb(M3(f4v(rb.s0), f4v(rb.s1), f4v(rb.s2)), f4v(rb.so));
+    Manifold *none = nullptr;
+    result[t] = solve_static<true>(sa, xa, sb, xb, *none, nullptr) ? 1u : 0u;
+}
+
 __global__ void k_area_clear_moved(uint32_t n, AreaRec *areas) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) areas[i].flags &= ~AF_MOVED;
@@ -156,6 +168,8 @@ static int afail(bpc_context *ctx, const char *msg) {
     ctx->err = g_area_msg.c_str();
     return -1;
 }
+
+static int aa_resolve(bpc_context *ctx);
 
 static void mul_xf(const float *a, const float *b, float *o) { // Transform3D product, rows + origin, fp32 like the reference
     for (int r = 0; r < 3; r++) {
@@ -247,6 +261,20 @@ extern "C" int bpc_areas_destroy(bpc_context *ctx, const int32_t *areas, int n) 
     for (int i = 0; i < n; i++) {
         AreaRec &r = ctx->h_areas[areas[i]];
         if (!(r.flags & AF_ALIVE)) continue;
+        // its pair objects go: whoever watched it hears it leave (bradot_area_pair_3d.cpp:195-206); it hears nothing itself
+        if (aa_resolve(ctx)) return -1;
+        {
+            std::vector<uint64_t> keep;
+            for (uint64_t key : ctx->aa_colliding) {
+                uint32_t w = (uint32_t)(key >> 32), o = (uint32_t)key;
+                if (w != (uint32_t)areas[i] && o != (uint32_t)areas[i]) {
+                    keep.push_back(key);
+                } else if (o == (uint32_t)areas[i] && (ctx->h_areas[w].flags & AF_AREA_MONITOR_CB) && (r.flags & AF_MONITORABLE)) {
+                    ctx->h_area_events_pending.push_back(make_uint4(w, o, 3u, 0u));
+                }
+            }
+            ctx->aa_colliding.swap(keep);
+        }
         r.flags &= ~AF_ALIVE;
         ctx->n_areas_alive--;
         if (ctx->body_area_cnt.p && ctx->body_area_cap) {
@@ -256,6 +284,38 @@ extern "C" int bpc_areas_destroy(bpc_context *ctx, const int32_t *areas, int n) 
     }
     BPC_CHECK(cudaGetLastError());
     ctx->areas_dirty = true;
+    return 0;
+}
+
+// One direction of an area pair changed (or is cut): keep the sorted set, raise the event if the watcher has an area monitor
+// callback and the other is monitorable (bradot_area_pair_3d.cpp:137-152, 195-206).  status 2 = area entered, 3 = area left.
+static void aa_set(bpc_context *ctx, uint32_t watcher, uint32_t other, bool now, uint32_t watcher_flags, uint32_t other_flags) {
+    uint64_t key = ((uint64_t)watcher << 32) | other;
+    auto it = std::lower_bound(ctx->aa_colliding.begin(), ctx->aa_colliding.end(), key);
+    bool was = it != ctx->aa_colliding.end() && *it == key;
+    if (was == now) return;
+    if (now) ctx->aa_colliding.insert(it, key);
+    else ctx->aa_colliding.erase(it);
+    if ((watcher_flags & AF_AREA_MONITOR_CB) && (other_flags & AF_MONITORABLE)) ctx->h_area_events_pending.push_back(make_uint4(watcher, other, now ? 2u : 3u, 0u));
+}
+
+// the overlap bytes of the last step's candidates are in: BradotArea2Pair3D::setup / pre_solve for each of them
+static int aa_resolve(bpc_context *ctx) {
+    if (!ctx->aa_launched) return 0;
+    ctx->aa_launched = false;
+    size_t n = ctx->aa_cand.size();
+    std::vector<uint32_t> res(n);
+    BPC_CHECK(cudaMemcpyAsync(res.data(), ctx->aa_result.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BPC_CHECK(cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < n; i++) {
+        const bpc_context::AreaPairCand &c = ctx->aa_cand[i];
+        if (c.a >= ctx->h_areas.size() || c.b >= ctx->h_areas.size() || !(ctx->h_areas[c.a].flags & AF_ALIVE) || !(ctx->h_areas[c.b].flags & AF_ALIVE)) continue;
+        bool result_a = (c.layer_b & c.mask_a) != 0, result_b = (c.layer_a & c.mask_b) != 0;
+        if (!res[i]) result_a = result_b = false;
+        aa_set(ctx, c.a, c.b, result_a, c.flags_a, c.flags_b);
+        aa_set(ctx, c.b, c.a, result_b, c.flags_b, c.flags_a);
+    }
+    ctx->aa_cand.clear();
     return 0;
 }
 
@@ -315,6 +375,27 @@ int bpc_flush_area_tables(bpc_context *ctx) {
         BPC_CHECK(cudaMemcpyAsync(ctx->area_list.p, list.data(), na * 4, cudaMemcpyHostToDevice, st));
         BPC_CHECK(cudaMemcpyAsync(ctx->area_start.p, start.data(), (ns + 1) * 4, cudaMemcpyHostToDevice, st));
         BPC_CHECK(cudaStreamSynchronize(st)); // host vectors go out of scope
+        // area pairs the coming step looks at: both alive, same space, one of them moved, one of them monitorable (two
+        // areas that are not sit in the static tree and never pair)
+        if (aa_resolve(ctx)) return -1;
+        for (size_t s = 0; s < ns; s++) {
+            for (uint32_t p = start[s]; p < start[s + 1]; p++) {
+                for (uint32_t q = p + 1; q < start[s + 1]; q++) {
+                    const AreaRec &ra = ctx->h_areas[list[p]], &rb = ctx->h_areas[list[q]];
+                    if (!(ra.flags & rb.flags & AF_ALIVE) || !((ra.flags | rb.flags) & AF_MOVED) || !((ra.flags | rb.flags) & AF_MONITORABLE)) continue;
+                    ctx->aa_cand.push_back({ list[p], list[q], ra.flags, rb.flags, ra.layer, ra.mask, rb.layer, rb.mask });
+                }
+            }
+        }
+        if (!ctx->aa_cand.empty()) {
+            std::vector<uint2> pr(ctx->aa_cand.size());
+            for (size_t i = 0; i < pr.size(); i++) pr[i] = make_uint2(ctx->aa_cand[i].a, ctx->aa_cand[i].b);
+            ctx->aa_pairs.reserve(pr.size(), false, st);
+            ctx->aa_result.reserve(pr.size(), false, st);
+            if (!ctx->aa_pairs.p || !ctx->aa_result.p) return afail(ctx, "areas: out of device memory");
+            BPC_CHECK(cudaMemcpyAsync(ctx->aa_pairs.p, pr.data(), pr.size() * sizeof(uint2), cudaMemcpyHostToDevice, st));
+            BPC_CHECK(cudaStreamSynchronize(st));
+        }
         // the moved flags travelled with the records; they are spent by the coming step
         for (AreaRec &r : ctx->h_areas) r.flags &= ~AF_MOVED;
     }
@@ -346,6 +427,12 @@ int bpc_launch_areas(bpc_context *ctx) {
     a.counters = ctx->counters.p;
     k_area_pairs<<<(ctx->n_bodies + 127) / 128, 128, 0, st>>>(a);
     ctx->launches += 1;
+    if (!ctx->aa_cand.empty() && !ctx->aa_launched) {
+        uint32_t n = (uint32_t)ctx->aa_cand.size();
+        k_area_area<<<(n + 63) / 64, 64, 0, st>>>(a, n, ctx->aa_pairs.p, ctx->aa_result.p);
+        ctx->launches += 1;
+        ctx->aa_launched = true;
+    }
     if (ctx->areas_moved) {
         uint32_t na = (uint32_t)ctx->h_areas.size();
         k_area_clear_moved<<<(na + 127) / 128, 128, 0, st>>>(na, ctx->d_areas.p);
@@ -383,6 +470,7 @@ extern "C" int bpc_area_events_read(bpc_context *ctx, bpc_area_event *out, int m
     if (max_events < 0 || (max_events > 0 && !out)) return afail(ctx, "bpc_area_events_read: bad arguments");
     BPC_CHECK(cudaSetDevice(ctx->device));
     BPC_CHECK(cudaStreamSynchronize(ctx->stream));
+    if (aa_resolve(ctx)) return -1;
     uint32_t n_dev = ctx->area_events.p ? std::min(ctx->h_counters[CNT_AREA_EVENTS], (uint32_t)AREA_EVENT_CAP) : 0u;
     std::vector<uint4> ev(ctx->h_area_events_pending);
     ctx->h_area_events_pending.clear();

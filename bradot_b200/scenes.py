@@ -35,7 +35,7 @@ AREA_DT = np.dtype([("space", "<i4"), ("shape", "<i4"), ("flags", "<u4"), ("prio
                     ("layer", "<u4"), ("mask", "<u4"), ("gravity_mode", "<i4"), ("linear_damp_mode", "<i4"), ("angular_damp_mode", "<i4"),
                     ("gravity", "<f4"), ("gravity_vector", "<f4", 3), ("point_unit_distance", "<f4"), ("linear_damp", "<f4"),
                     ("angular_damp", "<f4"), ("reserved", "<u4")])
-AREA_MONITORABLE, AREA_MONITOR_CB, AREA_GRAVITY_POINT = 1, 2, 4
+AREA_MONITORABLE, AREA_MONITOR_CB, AREA_GRAVITY_POINT, AREA_AREA_MONITOR_CB = 1, 2, 4, 8
 JOINT_NO_COLLIDE, JOINT_USE_LIMIT, JOINT_ENABLE_MOTOR, JOINT_HAS_PARAMS = 1, 2, 4, 8
 PIN_DEFAULTS = np.array([0.3, 1.0, 0.0, 0, 0, 0, 0, 0], np.float32)
 HINGE_DEFAULTS = np.array([0.3, -np.pi, np.pi, 0.3, 0.9, 1.0, 0.0, 0.0], np.float32)   # upper = -pi, lower = pi: the reference's "no limit"
@@ -686,6 +686,14 @@ def area_zones():
     sc.add_areas(1, shape=zone, xf=at(35.0, 3.0, 0.0), linear_damp_mode=3, linear_damp=8.0, flags=AREA_MONITOR_CB)
     sc.add_bodies(1, shape=ball, xf=at(40.0, 4.5, 0.0), flags=0)
     sc.add_areas(1, shape=zone, xf=at(40.0, 3.0, 0.0), gravity_mode=3, gravity=0.5, gravity_vector=(0, 1, 0), flags=AREA_MONITOR_CB)
+    # column H (x = 50): areas watching areas.  12 watches and can be watched, 13 can only be watched, 14 only watches, 15 does
+    # both but on a layer nobody's mask meets; 16 overlaps 12 from the start.  The script moves 13, 14 and 15 onto 12.
+    both = AREA_MONITORABLE | AREA_AREA_MONITOR_CB
+    sc.add_areas(1, shape=zone, xf=at(50.0, 3.0, 0.0), flags=both)
+    sc.add_areas(1, shape=slab, xf=at(50.0, 9.0, 0.0), flags=AREA_MONITORABLE)
+    sc.add_areas(1, shape=well, xf=at(56.0, 3.0, 0.0), flags=AREA_AREA_MONITOR_CB)
+    sc.add_areas(1, shape=zone, xf=at(50.0, -6.0, 0.0), flags=both, layer=8, mask=8)
+    sc.add_areas(1, shape=tube, xf=at(50.8, 3.0, 0.3, 0.4), flags=both)
     sc.bodies["mask"] = 0          # no body collides with any other: free flight only (an area looks at the body's LAYER)
     return sc
 
@@ -708,4 +716,15 @@ def area_zones_script():
     away = IDENT12.copy()
     away[9], away[10], away[11] = 5.0, 30.0, 0.0
     add(70, 3, 6, away)           # the sideways zone of column B is taken away while bodies may still be in it
+
+    def place(x, y, z):
+        f = IDENT12.copy()
+        f[9], f[10], f[11] = x, y, z
+        return f
+    add(20, 13, 6, place(50.0, 3.5, 0.0))     # the watched-only slab comes down into 12 (and 16): both hear it, it hears nothing
+    add(30, 14, 6, place(52.5, 3.0, 0.0))     # the watch-only well reaches 12, 13 and 16: it hears all three, none hears it
+    add(45, 15, 6, place(50.0, 3.0, 0.0))     # layer 8 meets nobody's mask: silence both ways
+    add(60, 13, 6, place(50.0, 9.0, 0.0))     # the slab leaves again
+    add(90, 16, 7)                            # the tube is freed inside 12: 12 and the well hear it leave
+    add(100, 12, 6, place(50.0, 20.0, 0.0))   # 12 itself moves off: it leaves the well
     return ev

@@ -1512,7 +1512,8 @@ void BradotPhysicsServerCUDA::_fill_area_desc(const Area *p_area, bpc_area_desc 
 	Shape *shape = shape_owner.get_or_null(p_area->shape);
 	r_desc.space = space ? space->handle : -1;
 	r_desc.shape = shape ? _shape_handle(shape) : -1;
-	r_desc.flags = (p_area->monitorable ? 1u : 0u) | (p_area->monitor_callback.is_valid() ? 2u : 0u) | (p_area->gravity_is_point ? 4u : 0u);
+	r_desc.flags = (p_area->monitorable ? 1u : 0u) | (p_area->monitor_callback.is_valid() ? 2u : 0u) | (p_area->gravity_is_point ? 4u : 0u) |
+			(p_area->area_monitor_callback.is_valid() ? 8u : 0u);
 	r_desc.priority = p_area->priority;
 	_xf_to_floats(p_area->xf, r_desc.xf);
 	_xf_to_floats(p_area->shape_xf, r_desc.shape_xf);
@@ -1558,6 +1559,10 @@ void BradotPhysicsServerCUDA::_area_leave_space(Area *p_area) {
 	if (p_area->handle >= 0) {
 		int32_t h = p_area->handle;
 		ERR_FAIL_COND_MSG(bpc_areas_destroy(ctx, &h, 1) < 0, bpc_last_error(ctx));
+		FreedBody fa; // an area that watched it still has to be told who left
+		fa.rid = p_area->self;
+		fa.instance_id = p_area->instance_id;
+		freed_areas[h] = fa;
 		area_of_handle[h] = nullptr;
 		p_area->handle = -1;
 	}
@@ -1806,9 +1811,7 @@ void BradotPhysicsServerCUDA::area_set_area_monitor_callback(RID p_area, const C
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
 	area->area_monitor_callback = p_callback.is_valid() ? p_callback : Callable();
-	if (p_callback.is_valid()) {
-		WARN_PRINT_ONCE("BradotPhysicsCUDA: areas do not monitor other areas yet (BradotArea2Pair3D is not built); the callback is kept and never called.");
-	}
+	_area_changed(area);
 }
 
 void BradotPhysicsServerCUDA::area_set_ray_pickable(RID p_area, bool p_enable) {
@@ -1834,17 +1837,18 @@ void BradotPhysicsServerCUDA::_flush_area_events() {
 	}
 	if (n <= 0) {
 		freed_bodies.clear();
+		freed_areas.clear();
 		return;
 	}
-	HashMap<uint64_t, int> state; // (area << 32 | body) -> entered minus left
+	HashMap<uint64_t, int> state; // (area << 32 | body or other area, bit 31 = other area) -> entered minus left
 	LocalVector<uint64_t> order;
 	for (int i = 0; i < n && i < (int)ev.size(); i++) {
-		uint64_t key = ((uint64_t)(uint32_t)ev[i].area << 32) | (uint32_t)ev[i].body;
+		uint64_t key = ((uint64_t)(uint32_t)ev[i].area << 32) | (uint32_t)ev[i].body | (ev[i].status >= 2 ? 0x80000000u : 0u);
 		if (!state.has(key)) {
 			state[key] = 0;
 			order.push_back(key);
 		}
-		state[key] += ev[i].status == 0 ? 1 : -1;
+		state[key] += (ev[i].status & 1) == 0 ? 1 : -1;
 	}
 	for (uint64_t key : order) {
 		int s = state[key];
@@ -1852,9 +1856,35 @@ void BradotPhysicsServerCUDA::_flush_area_events() {
 			continue;
 		}
 		uint32_t ai = (uint32_t)(key >> 32);
-		int32_t slot = (int32_t)(uint32_t)key;
 		Area *area = ai < area_of_handle.size() ? area_of_handle[ai] : nullptr;
-		if (!area || !area->monitor_callback.is_valid()) {
+		if (!area) {
+			continue;
+		}
+		if (key & 0x80000000u) { // an area entered / left: the area monitor callback (P3D/bradot_area_3d.cpp:273-310)
+			uint32_t oi = (uint32_t)key & 0x7fffffffu;
+			if (!area->area_monitor_callback.is_valid()) {
+				continue;
+			}
+			RID other_rid;
+			ObjectID other_id;
+			if (oi < area_of_handle.size() && area_of_handle[oi]) {
+				other_rid = area_of_handle[oi]->self;
+				other_id = area_of_handle[oi]->instance_id;
+			} else if (freed_areas.has((int32_t)oi)) {
+				other_rid = freed_areas[(int32_t)oi].rid;
+				other_id = freed_areas[(int32_t)oi].instance_id;
+			} else {
+				continue;
+			}
+			Variant res[5] = { s > 0 ? AREA_BODY_ADDED : AREA_BODY_REMOVED, other_rid, other_id, 0, 0 };
+			const Variant *resptr[5] = { &res[0], &res[1], &res[2], &res[3], &res[4] };
+			Callable::CallError ce;
+			Variant ret;
+			area->area_monitor_callback.callp(resptr, 5, ret, ce);
+			continue;
+		}
+		int32_t slot = (int32_t)(uint32_t)key;
+		if (!area->monitor_callback.is_valid()) {
 			continue;
 		}
 		RID body_rid;
@@ -1879,6 +1909,7 @@ void BradotPhysicsServerCUDA::_flush_area_events() {
 		}
 	}
 	freed_bodies.clear();
+	freed_areas.clear();
 }
 
 void BradotPhysicsServerCUDA::free(RID p_rid) {

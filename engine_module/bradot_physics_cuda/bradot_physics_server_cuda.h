@@ -187,7 +187,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	mutable RID_PtrOwner<Area, true> area_owner;
 	LocalVector<Area *> pending_areas, dirty_areas;
 	LocalVector<Area *> area_of_handle;
-	HashMap<int32_t, FreedBody> freed_bodies;
+	HashMap<int32_t, FreedBody> freed_bodies, freed_areas;
 	void _area_changed(Area *p_area);
 	void _area_leave_space(Area *p_area);
 	void _fill_area_desc(const Area *p_area, bpc_area_desc &r_desc);

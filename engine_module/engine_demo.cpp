@@ -63,6 +63,20 @@ static void on_area_monitor(int p_status, const RID &p_body, ObjectID p_instance
 	g_area_events.push_back(p_status);
 }
 
+static std::vector<RID> *g_area_rids = nullptr;
+static void on_area_area_monitor(int p_status, const RID &p_other, ObjectID p_instance, int p_other_shape, int p_area_shape, int p_area) {
+	int idx = -1;
+	for (size_t k = 0; g_area_rids && k < g_area_rids->size(); k++) {
+		if ((*g_area_rids)[k] == p_other) {
+			idx = (int)k;
+		}
+	}
+	g_area_events.push_back(g_flushed_step);
+	g_area_events.push_back(p_area);
+	g_area_events.push_back(idx);
+	g_area_events.push_back(2 + p_status);
+}
+
 // what the state-sync callbacks reported: last transform per body, number of calls
 static std::vector<Transform3D> g_synced;
 static std::vector<int> g_sync_calls;
@@ -274,6 +288,7 @@ int main(int argc, char **argv) {
 	std::vector<RID> area_r;
 	std::vector<char> area_freed;
 	g_body_rids = &body_r;
+	g_area_rids = &area_r;
 	for (uint32_t i = 0; i < hd.n_areas; i++) {
 		const ScnArea &a = sareas[i];
 		RID ar = ps->area_create();
@@ -294,6 +309,9 @@ int main(int argc, char **argv) {
 		ps->area_set_monitorable(ar, (a.flags & 1) != 0);
 		if (a.flags & 2) {
 			ps->area_set_monitor_callback(ar, callable_mp_static(&on_area_monitor).bind((int)i));
+		}
+		if (a.flags & 8) {
+			ps->area_set_area_monitor_callback(ar, callable_mp_static(&on_area_area_monitor).bind((int)i));
 		}
 		ps->area_set_space(ar, space_r[a.space]);
 		area_r.push_back(ar);

@@ -195,9 +195,11 @@ int bpc_contacts_read(bpc_context *ctx, int32_t *counts, int32_t *offsets, bpc_c
  * in a space that bodies overlap: one with a space override changes the gravity / damping of the bodies standing in it
  * (by priority, with the reference's combine / replace rules), one with a monitor callback is told who enters and leaves.
  * flags: bit0 monitorable, bit1 a body monitor callback is set (events are raised), bit2 the gravity vector is a point
- * (in the area's space) bodies are pulled towards, bit3 reserved (area monitor callback).  Override modes are
+ * (in the area's space) bodies are pulled towards, bit3 an area monitor callback is set (it is told which monitorable
+ * areas it overlaps: BradotArea2Pair3D, P3D/bradot_area_pair_3d.cpp:124-206; looked at in steps where one of the two moved).
+ * Override modes are
  * PhysicsServer3D::AreaSpaceOverrideMode: 0 disabled, 1 combine, 2 combine-replace, 3 replace, 4 replace-combine.
- * Not built: area-against-area monitoring (BradotArea2Pair3D), wind (soft bodies only). */
+ * Not built: wind (soft bodies only). */
 typedef struct bpc_area_desc {
     int32_t space, shape;
     uint32_t flags;
@@ -209,7 +211,7 @@ typedef struct bpc_area_desc {
     uint32_t reserved;
 } bpc_area_desc;
 typedef struct bpc_area_event {
-    int32_t area, body, status; /* status: 0 = AREA_BODY_ADDED, 1 = AREA_BODY_REMOVED */
+    int32_t area, body, status; /* status 0 / 1: body `body` entered / left the area; 2 / 3: AREA `body` entered / left it */
 } bpc_area_event;
 int bpc_areas_create(bpc_context *ctx, const bpc_area_desc *descs, int n);              /* -> index of the first */
 int bpc_areas_write(bpc_context *ctx, int first, int n, const bpc_area_desc *descs);    /* any area_set_*: also "the area moved" */

@@ -64,6 +64,7 @@ public:
 };
 
 // ---------------------------------------------------------------- scene file
+
 #pragma pack(push, 1)
 struct ScnHeader {
 	char magic[4]; // "BSCN"
@@ -126,6 +127,14 @@ static void on_area_monitor(int p_status, const RID &p_body, ObjectID p_instance
 	g_area_events.push_back(p_area);
 	g_area_events.push_back(it == g_body_of_rid.end() ? -1 : it->second);
 	g_area_events.push_back(p_status);
+}
+// ... and the area monitor callbacks: (area, other area, 2 + status)
+static std::map<uint64_t, int> g_area_of_rid;
+static void on_area_area_monitor(int p_status, const RID &p_other, ObjectID p_instance, int p_other_shape, int p_area_shape, int p_area) {
+	auto it = g_area_of_rid.find(p_other.get_id());
+	g_area_events.push_back(p_area);
+	g_area_events.push_back(it == g_area_of_rid.end() ? -1 : it->second);
+	g_area_events.push_back(2 + p_status);
 }
 
 static Transform3D xf_from(const float *f) {
@@ -962,6 +971,10 @@ int main(int argc, char **argv) {
 		if (a.flags & 2) {
 			ps->area_set_monitor_callback(ar, callable_mp_static(&on_area_monitor).bind((int)i));
 		}
+		if (a.flags & 8) {
+			ps->area_set_area_monitor_callback(ar, callable_mp_static(&on_area_area_monitor).bind((int)i));
+		}
+		g_area_of_rid[ar.get_id()] = (int)i;
 		ps->area_set_space(ar, w.spaces[a.space]);
 		w.areas.push_back(ar);
 		w.area_freed.push_back(0);

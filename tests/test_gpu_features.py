@@ -351,7 +351,7 @@ def _apply_area_events(ps, sc, areas, events, step, gone_bodies, gone_areas):
 def test_areas_overrides_and_monitoring_follow_the_reference():
     """Areas (bradot_area_pair_3d.cpp:36-118, the area loop of integrate_forces bradot_body_3d.cpp:498-585,
     compute_gravity bradot_area_3d.cpp:312-332, call_queries :232-310): scenes.area_zones() free-running beside the reference
-    running the same script.  No body ever touches another, so the two runs differ by rounding only: after EVERY step the
+    running the same script; BradotArea2Pair3D (:124-206) for the areas that watch areas.  No body ever touches another, so the two runs differ by rounding only: after EVERY step the
     enter / exit events told to the monitor callbacks are the same set, and positions and velocities agree to 1e-4."""
     _need_oracle()
     sc = scenes.area_zones()
@@ -362,7 +362,7 @@ def test_areas_overrides_and_monitoring_follow_the_reference():
     areas = sc.areas.copy()
     kin = np.nonzero(sc.bodies["mode"] == scenes.MODE_KINEMATIC)[0]
     gone_b, gone_a = set(), set()
-    seen = {0: 0, 1: 0}
+    seen = {0: 0, 1: 0, 2: 0, 3: 0}
     for k in range(1, steps + 1):
         _apply_area_events(ps, sc, areas, events, k, gone_b, gone_a)
         for row in dump.get(("kin_targets", k), ()):
@@ -381,7 +381,7 @@ def test_areas_overrides_and_monitoring_follow_the_reference():
         if k == 45:      # the zone was moved onto the sleeping box at step 40: attached to it, and the box sleeps on
             inside, attached = ps.body_areas(13)
             assert list(inside) == [9] and attached.all() and st[13, 18] == 0
-    assert seen[0] >= 10 and seen[1] >= 8, seen
+    assert seen[0] >= 10 and seen[1] >= 8 and seen[2] >= 7 and seen[3] >= 6, seen     # 2 / 3: an AREA entered / left a watching area
     # what the override did: the ball in the well was pulled off its vertical line, the box under the moved zone rose once woken
     st = ps.bodies_read_state()
     assert abs(st[5, 9] - 10.0) > 0.05 and st[13, 10] > 3.05
