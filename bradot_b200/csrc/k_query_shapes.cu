@@ -689,3 +689,301 @@ extern "C" int bpc_space_cast_motions(bpc_context *ctx, int space, int n, const 
     BPC_CHECK(cudaStreamSynchronize(st));
     return 0;
 }
+
+// ---- body_test_motion (bradot_space_3d.cpp:619-1029): recover, cast, rest -- one thread per request
+struct MtArgs {
+    QsArgs q;
+    const bpc_motion_params *params;
+    bpc_motion_result *out;
+    const uint32_t *shape_id;
+    const uint64_t *except_keys;
+    uint32_t n_except, n_bodies;
+};
+
+// _cull_aabb_for_body's filter (:619-649) on one candidate: not the body itself, its layer meets the body's mask, no
+// collision exception either way, not on the query exclude list.  (Areas are not in the tree.)
+__device__ inline bool mt_body(const MtArgs &m, uint32_t self, uint32_t self_mask, uint32_t j, Sh &sb, X3 &xb) {
+    const QsArgs &a = m.q;
+    if (j == self) return false;
+    uint4 mj = a.meta[j];
+    if (mj.w != a.space || !(mj.y & self_mask)) return false;
+    if (a.ex.n && q_excluded(a.ex, j)) return false;
+    if (m.n_except) {
+        uint64_t key = ((uint64_t)min(self, j) << 32) | max(self, j);
+        uint32_t lo = 0, hi = m.n_except;
+        while (lo < hi) {
+            uint32_t mid = (lo + hi) >> 1;
+            if (m.except_keys[mid] < key) lo = mid + 1;
+            else hi = mid;
+        }
+        if (lo < m.n_except && m.except_keys[lo] == key) return false;
+    }
+    BodyXf bx = a.xf[j];
+    xb = X3(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
+    if (!((mj.x >> 8) & BF_SHAPE_IDENT)) {
+        BodyXf sx = a.shape_xf[j];
+        xb = xb * X3(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+    }
+    sb = qs_shape(a, mj.x >> 24, a.shape_p[j]);
+    return true;
+}
+
+// STEP 3 of body_test_motion as a function of its own: the contacts of shape `bs` at `bsx` with everything in [bmin, bmax]
+__device__ __noinline__ void mt_rest_contacts(const MtArgs *m, const QsArgs *a, uint32_t self, uint32_t self_mask, const Sh *bs, const X3 *bsx, V3 bmin,
+                                              V3 bmax, float margin, RestSink *rcd) {
+    qs_for_candidates(*a, bmin, bmax, [&](uint32_t j) {
+        Sh sb;
+        X3 xb;
+        if (!mt_body(*m, self, self_mask, j, sb, xb)) return;
+        rcd->cur_body = j;
+        Manifold *none = nullptr;
+        solve_static<false, true>(*bs, *bsx, sb, xb, *none, nullptr, nullptr, rcd, margin, 0.f);
+    });
+}
+
+// STEP 1's collection, likewise: the contact pairs (margin variants, the collecting callback) of the body where it stands.
+// (Both steps are functions of their own on purpose: inlined into the one large kernel, the plane routine was seen to read
+// another transform than the one handed to it -- a build-dependent effect that went away with the call boundary.)
+__device__ __noinline__ void mt_recover_contacts(const MtArgs *m, const QsArgs *a, uint32_t self, uint32_t self_mask, const Sh *bs, const X3 *bsx, V3 bmin,
+                                                 V3 bmax, float margin, RawSink *sink) {
+    qs_for_candidates(*a, bmin, bmax, [&](uint32_t j) {
+        Sh sb;
+        X3 xb;
+        if (!mt_body(*m, self, self_mask, j, sb, xb)) return;
+        Manifold *none = nullptr;
+        solve_static<false, true>(*bs, *bsx, sb, xb, *none, nullptr, sink, nullptr, margin, 0.f);
+    });
+}
+
+#define MT_MAX_RECOVER 32
+__global__ void __launch_bounds__(32) k_test_motion(MtArgs m) {
+    QsArgs a = m.q; // per-thread copy: the space differs from request to request
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= a.n) return;
+    const bpc_motion_params prm = m.params[r];
+    bpc_motion_result res;
+    memset(&res, 0, sizeof(res));
+    const uint32_t self = (uint32_t)prm.body;
+    const uint4 ms = a.meta[self];
+    a.space = ms.w;
+    const V3 motion(prm.motion[0], prm.motion[1], prm.motion[2]);
+    const float margin = fmaxf(prm.margin, TEST_MOTION_MARGIN_MIN_VALUE);
+    const float min_contact_depth = margin * TEST_MOTION_MIN_CONTACT_DEPTH_FACTOR;
+    const float motion_length = length(motion);
+    X3 body_transform(M3(V3(prm.from[0], prm.from[1], prm.from[2]), V3(prm.from[3], prm.from[4], prm.from[5]), V3(prm.from[6], prm.from[7], prm.from[8])),
+                      V3(prm.from[9], prm.from[10], prm.from[11]));
+    const V3 from_origin = body_transform.o;
+    const Sh bs = qs_shape(a, ms.x >> 24, a.shape_p[self]);
+    X3 local; // the body's shape in its own frame
+    local.b = M3(V3(1, 0, 0), V3(0, 1, 0), V3(0, 0, 1));
+    local.o = V3();
+    if (!((ms.x >> 8) & BF_SHAPE_IDENT)) {
+        BodyXf sx = a.shape_xf[self];
+        local = X3(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+    }
+    const ShapeRec sr = a.shapes[m.shape_id[self]];
+    Box3 la;
+    la.pos = f4v(sr.aabb_pos);
+    la.size = f4v(sr.aabb_size);
+    auto body_box = [&](const X3 &bt, float grow, V3 &bmin, V3 &bmax) {
+        Box3 box = xform_aabb(bt * local, la);
+        bmin = box.pos - V3(grow, grow, grow);
+        bmax = box.pos + box.size + V3(grow, grow, grow);
+    };
+    bool recovered = false;
+    { // STEP 1: free the body if it is stuck (:704-789)
+        V3 sr_pts[MT_MAX_RECOVER * 2];
+        for (int attempt = 4; attempt > 0; attempt--) {
+            RawSink sink;
+            sink.pts = sr_pts;
+            sink.n = 0;
+            sink.max = MT_MAX_RECOVER;
+            V3 bmin, bmax;
+            body_box(body_transform, margin + 1e-4f, bmin, bmax);
+            const X3 bsx = body_transform * local;
+            mt_recover_contacts(&m, &a, self, ms.z, &bs, &bsx, bmin, bmax, margin, &sink);
+            if (sink.n == 0) break;
+            recovered = true;
+            // every obstacle has collision priority 1 here, so the weights (priorities[i] * inv_total_weight) are all 1
+            V3 recover_motion;
+            for (int i = 0; i < sink.n; i++) {
+                V3 pa = sr_pts[i * 2 + 0], pb = sr_pts[i * 2 + 1];
+                V3 n = normalized(pa - pb);
+                float d = dot(n, pb);
+                float depth = dot(n, pa + recover_motion) - d;
+                if ((double)depth > (double)min_contact_depth + BPC_CMP_EPSILON) {
+                    recover_motion -= n * (depth - min_contact_depth) * 0.4f * 1.0f * 1.0f;
+                }
+            }
+            if (recover_motion == V3()) break;
+            body_transform.o += recover_motion;
+        }
+    }
+    float safe = 1.0f, unsafe = 1.0f;
+    bool have_shape = false; // best_shape != -1
+    { // STEP 2: attempt the motion (:795-927)
+        V3 bmin, bmax;
+        body_box(body_transform, margin + 1e-4f, bmin, bmax);
+        V3 lo = bmin + motion, hi = bmax + motion;
+        bmin = V3(fminf(bmin.x, lo.x), fminf(bmin.y, lo.y), fminf(bmin.z, lo.z));
+        bmax = V3(fmaxf(bmax.x, hi.x), fmaxf(bmax.y, hi.y), fmaxf(bmax.z, hi.z));
+        GjkBody A;
+        A.s = bs;
+        A.x = body_transform * local;
+        const X3 inv = affine_inverse(A.x);
+        bool stuck = false;
+        float best_safe = 1, best_unsafe = 1;
+        qs_for_candidates(a, bmin, bmax, [&](uint32_t j) {
+            if (stuck) return;
+            GjkBody B;
+            if (!mt_body(m, self, ms.z, j, B.s, B.x)) return;
+            B.motion = V3();
+            B.swept = false;
+            V3 pA, pB;
+            A.swept = true;
+            A.motion = xform(inv.b, motion);
+            if (solve_distance(A, B, pA, pB)) return; // free all the way
+            A.swept = false;
+            if (!solve_distance(A, B, pA, pB)) { // overlapping where it stands
+                stuck = true;
+                return;
+            }
+            A.swept = true;
+            float low = 0.0f, high = 1.0f, coeff = 0.5f;
+            for (int k = 0; k < 8; k++) {
+                float fraction = low + (high - low) * coeff;
+                A.motion = xform(inv.b, motion * fraction);
+                V3 lA, lB;
+                bool collided = !solve_distance(A, B, lA, lB);
+                if (collided) {
+                    high = fraction;
+                    coeff = ((k == 0) || (low > 0.0f)) ? 0.5f : 0.25f;
+                } else {
+                    low = fraction;
+                    coeff = ((k == 0) || (high < 1.0f)) ? 0.5f : 0.75f;
+                }
+            }
+            if (low < best_safe) {
+                best_safe = low;
+                best_unsafe = high;
+            }
+        });
+        if (stuck) {
+            safe = 0;
+            unsafe = 0;
+            have_shape = true;
+        } else if (best_safe != 1.0f && best_safe < safe) {
+            safe = best_safe;
+            unsafe = best_unsafe;
+            have_shape = true;
+        }
+    }
+    bool collided = false;
+    if (((prm.flags & 2u) && recovered) || (safe < 1)) { // STEP 3: the contacts at the unsafe advance (:929-1012)
+        X3 ugt = body_transform;
+        ugt.o += motion * unsafe;
+        RestResult others[BPC_MAX_MOTION_COLLISIONS];
+        RestSink rcd;
+        rcd.best_len = 0.f;
+        rcd.best_body = 0xffffffffu;
+        rcd.contact = rcd.normal = V3();
+        int max_collisions = min(max(prm.max_collisions, 0), BPC_MAX_MOTION_COLLISIONS);
+        if (max_collisions > 1) {
+            rcd.max_results = max_collisions;
+            rcd.other = others;
+        }
+        rcd.min_allowed_depth = fminf(motion_length, min_contact_depth);
+        V3 bmin, bmax;
+        body_box(ugt, margin + 1e-4f, bmin, bmax);
+        const X3 bsx = ugt * local;
+        mt_rest_contacts(&m, &a, self, ms.z, &bs, &bsx, bmin, bmax, margin, &rcd);
+        if (rcd.result_count > 0) {
+            for (int ci = 0; ci < rcd.result_count; ci++) {
+                RestResult rr;
+                if (ci > 0) {
+                    rr = others[ci - 1];
+                } else {
+                    rr.len = rcd.best_len;
+                    rr.contact = rcd.contact;
+                    rr.normal = rcd.normal;
+                    rr.body = rcd.best_body;
+                }
+                bpc_motion_collision &c = res.collisions[ci];
+                c.collider = (int32_t)rr.body;
+                c.position[0] = rr.contact.x; c.position[1] = rr.contact.y; c.position[2] = rr.contact.z;
+                c.normal[0] = rr.normal.x; c.normal[1] = rr.normal.y; c.normal[2] = rr.normal.z;
+                c.depth = rr.len;
+                V3 v = qs_velocity_at(a, rr.body, rr.contact);
+                c.collider_velocity[0] = v.x; c.collider_velocity[1] = v.y; c.collider_velocity[2] = v.z;
+                if ((a.meta[rr.body].x & 0xffu) != MODE_STATIC) {
+                    float4 av = a.vel[rr.body].ang;
+                    c.collider_angular_velocity[0] = av.x; c.collider_angular_velocity[1] = av.y; c.collider_angular_velocity[2] = av.z;
+                }
+            }
+            V3 travel = safe * motion;
+            V3 remainder = motion - safe * motion;
+            travel += (body_transform.o - from_origin);
+            res.travel[0] = travel.x; res.travel[1] = travel.y; res.travel[2] = travel.z;
+            res.remainder[0] = remainder.x; res.remainder[1] = remainder.y; res.remainder[2] = remainder.z;
+            res.collision_safe_fraction = safe;
+            res.collision_unsafe_fraction = unsafe;
+            res.collision_count = rcd.result_count;
+            res.collision_depth = rcd.best_len;
+            collided = true;
+        }
+    }
+    (void)have_shape; // one shape per body: "the best shape" is the only one
+    if (!collided) {
+        V3 travel = motion;
+        travel += (body_transform.o - from_origin);
+        res.travel[0] = travel.x; res.travel[1] = travel.y; res.travel[2] = travel.z;
+        res.collision_safe_fraction = 1.0f;
+        res.collision_unsafe_fraction = 1.0f;
+        res.collision_depth = 0.0f;
+    }
+    res.collided = collided ? 1 : 0;
+    m.out[r] = res;
+}
+
+extern "C" int bpc_bodies_test_motion(bpc_context *ctx, int n, const bpc_motion_params *params, bpc_motion_result *out) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && (!params || !out))) {
+        ctx->err = "bpc_bodies_test_motion: bad arguments";
+        return -1;
+    }
+    for (int i = 0; i < n; i++) {
+        if (params[i].body < 0 || (uint32_t)params[i].body >= ctx->n_bodies || ctx->h_dead[params[i].body]) {
+            ctx->err = "bpc_bodies_test_motion: no such body";
+            return -1;
+        }
+        if (params[i].max_collisions < 0 || params[i].max_collisions > BPC_MAX_MOTION_COLLISIONS) {
+            ctx->err = "bpc_bodies_test_motion: max_collisions must be 0..32";
+            return -1;
+        }
+    }
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (bpc_flush_tables(ctx)) return -1;
+    if (bpc_build_tree(ctx)) return -1;
+    size_t p_words = ((size_t)n * sizeof(bpc_motion_params) / 4 + 3) & ~(size_t)3, r_words = (size_t)n * sizeof(bpc_motion_result) / 4;
+    ctx->staging.reserve(p_words + r_words + 16, false, st);
+    if (!ctx->staging.p) {
+        ctx->err = "bpc_bodies_test_motion: out of device memory";
+        return -1;
+    }
+    MtArgs m;
+    qs_fill(ctx, m.q, 0, n, 0xffffffffu);
+    m.params = (const bpc_motion_params *)ctx->staging.p;
+    m.out = (bpc_motion_result *)(ctx->staging.p + p_words);
+    m.shape_id = ctx->shape_id.p;
+    m.except_keys = ctx->except_keys.p;
+    m.n_except = ctx->n_except;
+    m.n_bodies = ctx->n_bodies;
+    BPC_CHECK(cudaMemcpyAsync((void *)m.params, params, (size_t)n * sizeof(bpc_motion_params), cudaMemcpyHostToDevice, st));
+    k_test_motion<<<(n + 31) / 32, 32, 0, st>>>(m);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaMemcpyAsync(out, m.out, (size_t)n * sizeof(bpc_motion_result), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}

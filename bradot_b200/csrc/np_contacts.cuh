@@ -134,18 +134,56 @@ __device__ inline void raw_add(RawSink &r, V3 pA, V3 pB) {
     }
 }
 
-// Where a query (rest_info) wants the deepest contact only: _rest_cbk_result with no list of other results
-// (bradot_space_3d.cpp:453-511) -- contacts shallower than min_allowed_depth are ignored, the longest A->B distance wins.
+// Where a query (rest_info, body_test_motion) wants the deepest contacts: _rest_cbk_result (bradot_space_3d.cpp:453-511) --
+// contacts shallower than min_allowed_depth are ignored, the longest A->B distance is the best result, and when a list of
+// other results is given the next deepest ones are kept in it (max_results counts the best one too).
+struct RestResult {
+    float len;
+    V3 contact, normal;
+    uint32_t body;
+};
 struct RestSink {
     float min_allowed_depth;
     float best_len;
     V3 contact, normal;
     uint32_t best_body, cur_body;
+    RestResult *other = nullptr;
+    int max_results = 0, result_count = 0;
 };
 __device__ inline void rest_add(RestSink &r, V3 pA, V3 pB, V3 normal) {
     float len = length(pB - pA);
     if (len < r.min_allowed_depth) return;
-    if (!(len > r.best_len)) return;
+    const bool is_best = len > r.best_len;
+    if (r.other && r.result_count > 0) {
+        int prev_count = r.result_count++; // a new result by default
+        int idx = 0;
+        float tested_len = is_best ? r.best_len : len;
+        for (; idx < prev_count - 1; ++idx) {
+            if (tested_len > r.other[idx].len) { // takes the place of a shallower one
+                r.result_count--;
+                break;
+            }
+        }
+        if (idx < r.max_results - 1) {
+            RestResult &o = r.other[idx];
+            if (is_best) { // the best so far steps down into the list
+                o.len = r.best_len;
+                o.contact = r.contact;
+                o.normal = r.normal;
+                o.body = r.best_body;
+            } else {
+                o.len = len;
+                o.contact = pB;
+                o.normal = normal;
+                o.body = r.cur_body;
+            }
+        } else {
+            r.result_count--; // no room: dropped
+        }
+    } else if (is_best) {
+        r.result_count = 1;
+    }
+    if (!is_best) return;
     r.best_len = len;
     r.contact = pB;
     r.normal = normal;

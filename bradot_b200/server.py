@@ -46,7 +46,7 @@ EXPORTS = [
     "bpc_bodies_set_max_contacts_reported", "bpc_body_read_contacts", "bpc_contacts_capacity", "bpc_contacts_read",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
     "bpc_space_set_query_exclude", "bpc_space_rest_infos", "bpc_space_cast_motions",
-    "bpc_areas_create", "bpc_areas_write", "bpc_areas_destroy", "bpc_area_count", "bpc_area_events_read", "bpc_body_read_areas",
+    "bpc_bodies_test_motion", "bpc_areas_create", "bpc_areas_write", "bpc_areas_destroy", "bpc_area_count", "bpc_area_events_read", "bpc_body_read_areas",
 ]
 STAGES = ("integrate_forces", "broadphase", "islands", "narrowphase", "schedule", "solve", "integrate_velocities")
 
@@ -63,6 +63,11 @@ class PhysicsError(RuntimeError):
 
 CONTACT_DT = np.dtype([("local_pos", "<f4", 3), ("depth", "<f4"), ("local_normal", "<f4", 3), ("collider", "<i4"), ("local_velocity", "<f4", 3),
                        ("collider_pos", "<f4", 3), ("collider_velocity", "<f4", 3), ("impulse", "<f4", 3)])
+MOTION_PARAMS_DT = np.dtype([("body", "<i4"), ("from", "<f4", 12), ("motion", "<f4", 3), ("margin", "<f4"), ("max_collisions", "<i4"), ("flags", "<u4")])
+MOTION_COLLISION_DT = np.dtype([("position", "<f4", 3), ("normal", "<f4", 3), ("collider_velocity", "<f4", 3), ("collider_angular_velocity", "<f4", 3),
+                                ("depth", "<f4"), ("collider", "<i4")])
+MOTION_RESULT_DT = np.dtype([("collided", "<i4"), ("collision_count", "<i4"), ("travel", "<f4", 3), ("remainder", "<f4", 3), ("collision_depth", "<f4"),
+                             ("collision_safe_fraction", "<f4"), ("collision_unsafe_fraction", "<f4"), ("collisions", MOTION_COLLISION_DT, 32)])
 REST_INFO_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("point", "<f4", 3), ("normal", "<f4", 3), ("linear_velocity", "<f4", 3)])
 RAY_RESULT_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("position", "<f4", 3), ("normal", "<f4", 3)])
 
@@ -114,6 +119,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
     lib.bpc_space_collide_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
     lib.bpc_space_set_query_exclude.argtypes = [vp, vp, ci]
+    lib.bpc_bodies_test_motion.argtypes = [vp, ci, vp, vp]
     lib.bpc_areas_create.argtypes = [vp, vp, ci]
     lib.bpc_areas_write.argtypes = [vp, ci, ci, vp]
     lib.bpc_areas_destroy.argtypes = [vp, vp, ci]
@@ -429,6 +435,13 @@ class PhysicsServerCUDA:
         n = self._check(self.lib.bpc_body_read_areas(self.ctx, int(slot), _ptr(out), 8))
         v = out[:min(n, 8)]
         return v & 0x3FFFFFFF, (v & 0x40000000) != 0
+
+    def bodies_test_motion(self, params):
+        """Batched PhysicsServer3D.body_test_motion: params MOTION_PARAMS_DT[n] -> MOTION_RESULT_DT[n]."""
+        p = np.ascontiguousarray(params, MOTION_PARAMS_DT)
+        out = np.zeros(len(p), MOTION_RESULT_DT)
+        self._check(self.lib.bpc_bodies_test_motion(self.ctx, len(p), _ptr(p), _ptr(out)))
+        return out
 
     def set_query_exclude(self, bodies):
         """Bodies every following space query skips (the `exclude` list of the query parameters); empty clears."""

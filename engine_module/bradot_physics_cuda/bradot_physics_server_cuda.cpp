@@ -1126,6 +1126,82 @@ PhysicsDirectBodyState3D *BradotPhysicsServerCUDA::body_get_direct_state(RID p_b
 	return body->direct_state;
 }
 
+
+// body_test_motion (P3D/bradot_physics_server_3d.cpp:903-916 -> BradotSpace3D::test_body_motion): one request through
+// bpc_bodies_test_motion; exclude_bodies and exclude_objects become the query exclude list for the duration of the call.
+bool BradotPhysicsServerCUDA::body_test_motion(RID p_body, const MotionParameters &p_parameters, MotionResult *r_result) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, false);
+	ERR_FAIL_COND_V(!body->space.is_valid(), false);
+	ERR_FAIL_COND_V(p_parameters.max_collisions < 0 || p_parameters.max_collisions > MotionResult::MAX_COLLISIONS, false);
+	_flush_pending();
+	if (r_result) {
+		*r_result = MotionResult();
+	}
+	if (body->slot < 0) { // no shape: nothing can stop it (test_body_motion's "no shapes found" exit)
+		if (r_result) {
+			r_result->travel = p_parameters.motion;
+		}
+		return false;
+	}
+	LocalVector<int32_t> excluded;
+	for (const RID &r : p_parameters.exclude_bodies) {
+		int32_t s = body_slot_of(r);
+		if (s >= 0) {
+			excluded.push_back(s);
+		}
+	}
+	if (!p_parameters.exclude_objects.is_empty()) {
+		for (uint32_t s = 0; s < body_of_slot.size(); s++) {
+			if (body_of_slot[s] && p_parameters.exclude_objects.has(body_of_slot[s]->instance_id)) {
+				excluded.push_back((int32_t)s);
+			}
+		}
+	}
+	if (!excluded.is_empty()) {
+		ERR_FAIL_COND_V_MSG(bpc_space_set_query_exclude(ctx, excluded.ptr(), (int)excluded.size()) < 0, false, bpc_last_error(ctx));
+	}
+	bpc_motion_params prm;
+	memset(&prm, 0, sizeof(prm));
+	prm.body = body->slot;
+	_xf_to_floats(p_parameters.from, prm.from);
+	prm.motion[0] = p_parameters.motion.x;
+	prm.motion[1] = p_parameters.motion.y;
+	prm.motion[2] = p_parameters.motion.z;
+	prm.margin = p_parameters.margin;
+	prm.max_collisions = p_parameters.max_collisions;
+	prm.flags = p_parameters.recovery_as_collision ? 2u : 0u;
+	bpc_motion_result res;
+	int rc = bpc_bodies_test_motion(ctx, 1, &prm, &res);
+	if (!excluded.is_empty()) {
+		bpc_space_set_query_exclude(ctx, nullptr, 0);
+	}
+	ERR_FAIL_COND_V_MSG(rc < 0, false, bpc_last_error(ctx));
+	if (r_result) {
+		r_result->travel = Vector3(res.travel[0], res.travel[1], res.travel[2]);
+		r_result->remainder = Vector3(res.remainder[0], res.remainder[1], res.remainder[2]);
+		r_result->collision_depth = res.collision_depth;
+		r_result->collision_safe_fraction = res.collision_safe_fraction;
+		r_result->collision_unsafe_fraction = res.collision_unsafe_fraction;
+		r_result->collision_count = res.collided ? res.collision_count : 0;
+		for (int i = 0; i < r_result->collision_count; i++) {
+			const bpc_motion_collision &c = res.collisions[i];
+			MotionCollision &o = r_result->collisions[i];
+			o.position = Vector3(c.position[0], c.position[1], c.position[2]);
+			o.normal = Vector3(c.normal[0], c.normal[1], c.normal[2]);
+			o.collider_velocity = Vector3(c.collider_velocity[0], c.collider_velocity[1], c.collider_velocity[2]);
+			o.collider_angular_velocity = Vector3(c.collider_angular_velocity[0], c.collider_angular_velocity[1], c.collider_angular_velocity[2]);
+			o.depth = c.depth;
+			o.local_shape = 0;
+			o.collider_shape = 0;
+			Body *other = (c.collider >= 0 && (uint32_t)c.collider < body_of_slot.size()) ? body_of_slot[c.collider] : nullptr;
+			o.collider = other ? other->self : RID();
+			o.collider_id = other ? other->instance_id : ObjectID();
+		}
+	}
+	return res.collided != 0;
+}
+
 // BradotBody3D::call_queries (bradot_body_3d.cpp:762-781): the force-integration callback, then the state-sync callback,
 // both handed the body's direct state
 void BradotPhysicsServerCUDA::_body_call_queries(Body *p_body) {

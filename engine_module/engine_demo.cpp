@@ -456,6 +456,25 @@ int main(int argc, char **argv) {
 		}
 		printf("%s[%.9g, %.9g, %d, %d, %.9g, %.9g, %.9g]", i ? ", " : "", (double)safe, (double)unsafe, idx, ridx, rest ? ri.point.x : 0.0, rest ? ri.point.y : 0.0, rest ? ri.point.z : 0.0);
 	}
+	// body_test_motion through the RID API: each of the first bodies pushed 0.4 m down from where it stands
+	printf("], \"motions\": [");
+	for (int i = 0; i < n_rays; i++) {
+		if (freed[i]) {
+			printf("%s[0, -1, 0, 0, 0, 0]", i ? ", " : "");
+			continue;
+		}
+		PhysicsServer3D::MotionParameters mp(Transform3D(ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM)), Vector3(0.05, -0.4, 0.0), 0.02);
+		mp.max_collisions = 4;
+		PhysicsServer3D::MotionResult mr;
+		bool hit = ps->body_test_motion(body_r[i], mp, &mr);
+		int idx = -1;
+		for (size_t k = 0; hit && k < body_r.size(); k++) {
+			if (body_r[k] == mr.collisions[0].collider) {
+				idx = (int)k;
+			}
+		}
+		printf("%s[%d, %d, %d, %.9g, %.9g, %.9g]", i ? ", " : "", hit ? 1 : 0, idx, mr.collision_count, (double)mr.collision_safe_fraction, (double)mr.travel.x, (double)mr.travel.y);
+	}
 	printf("]}\n");
 	fflush(stdout);
 	ps->finish();

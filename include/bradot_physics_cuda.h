@@ -332,6 +332,37 @@ int bpc_space_rest_infos(bpc_context *ctx, int space, int n, const int32_t *shap
 int bpc_space_cast_motions(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, const float *motions, float margin,
                            unsigned collision_mask, float *out_fractions, bpc_rest_info *out_info);
 
+/* PhysicsServer3D::body_test_motion (servers/physics_server_3d.h:525-571; P3D/bradot_space_3d.cpp:651-1029), batched: what
+ * CharacterBody3D's move_and_slide / move_and_collide ask.  Body `body`, placed at `from` instead of where the step left it,
+ * is (1) pushed out of what it overlaps (up to 4 rounds, 40 % of the excess depth each), (2) cast along `motion` (GJK distance
+ * on the swept shape, 8 bisection steps per obstacle) and (3) asked for up to max_collisions contacts where it stops (the
+ * margin variants of the collision routines, the reference's rest callback).  Obstacles: bodies of its space whose layer
+ * meets its mask, minus its collision exceptions and the query exclude list (bpc_space_set_query_exclude).
+ * flags: bit1 recovery_as_collision.  The order in which overlapping obstacles are visited is this backend's tree order; the
+ * recovery of step 1 is a sequential projection, so with several simultaneous contacts its result can differ from the
+ * reference's in the last digits of a millimetre. */
+#define BPC_MAX_MOTION_COLLISIONS 32
+typedef struct bpc_motion_params {
+    int32_t body;
+    float from[12];
+    float motion[3];
+    float margin;
+    int32_t max_collisions;
+    uint32_t flags;
+} bpc_motion_params;
+typedef struct bpc_motion_collision {
+    float position[3], normal[3], collider_velocity[3], collider_angular_velocity[3];
+    float depth;
+    int32_t collider;
+} bpc_motion_collision;
+typedef struct bpc_motion_result {
+    int32_t collided, collision_count;
+    float travel[3], remainder[3];
+    float collision_depth, collision_safe_fraction, collision_unsafe_fraction;
+    bpc_motion_collision collisions[BPC_MAX_MOTION_COLLISIONS];
+} bpc_motion_result;
+int bpc_bodies_test_motion(bpc_context *ctx, int n, const bpc_motion_params *params, bpc_motion_result *out);
+
 /* ---- utilities exposed for tests and tools */
 /* Sort n 64-bit keys on the device (the radix sort the broadphase uses); host in, host out. */
 int bpc_sort_u64(bpc_context *ctx, const uint64_t *keys_in, uint64_t *keys_out, int n);

@@ -661,6 +661,64 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 	d.arr("shape_query_xf", step, "f4", { (uint64_t)n, 12 }, sxf.data(), sxf.size() * 4);
 }
 
+// body_test_motion (bradot_space_3d.cpp:651-1029) for every third moving body of space 0, from where it stands (so it touches
+// its neighbours: the recovery step has work), along a direction and with parameters that depend on its index.  The requests
+// are dumped ("motion_queries": body, from(12), motion(3), margin, max_collisions, flags) with the answers ("motion_results":
+// collided, count, travel(3), remainder(3), depth, safe, unsafe, then 4 x (collider, position(3), normal(3), depth, velocity(3))).
+static void dump_motions(Dump &d, World &w, int step) {
+	std::map<RID, int> rid_index;
+	for (size_t i = 0; i < w.bodies.size(); i++) {
+		rid_index[w.bodies[i]] = (int)i;
+	}
+	std::vector<float> q, res;
+	uint64_t n = 0;
+	for (size_t i = 0; i < w.bodies.size() && n < 600; i += 3) {
+		if (w.body_freed[i] || w.body_space[i] != 0 || w.body_ptr[i]->get_mode() < PhysicsServer3D::BODY_MODE_KINEMATIC) {
+			continue;
+		}
+		PhysicsServer3D::MotionParameters mp;
+		mp.from = w.body_ptr[i]->get_transform();
+		float ang = 0.7f * (float)i;
+		float len = 0.05f + 0.15f * (float)(i % 5);
+		mp.motion = Vector3(Math::cos(ang) * len, ((i % 4) == 0 ? 0.5f : -0.5f) * len, Math::sin(ang) * len);
+		mp.margin = (i % 2) ? 0.04f : 0.001f;
+		mp.max_collisions = (i % 6) < 3 ? 1 : 4;
+		mp.recovery_as_collision = (i % 9) < 3;
+		PhysicsServer3D::MotionResult mr;
+		bool collided = w.ps->body_test_motion(w.bodies[i], mp, &mr);
+		q.push_back((float)i);
+		for (int r = 0; r < 3; r++) {
+			put3(q, mp.from.basis.rows[r]);
+		}
+		put3(q, mp.from.origin);
+		put3(q, mp.motion);
+		q.push_back(mp.margin);
+		q.push_back((float)mp.max_collisions);
+		q.push_back(mp.recovery_as_collision ? 2.f : 0.f);
+		res.push_back(collided ? 1.f : 0.f);
+		res.push_back((float)mr.collision_count);
+		put3(res, mr.travel);
+		put3(res, mr.remainder);
+		res.push_back(mr.collision_depth);
+		res.push_back(mr.collision_safe_fraction);
+		res.push_back(mr.collision_unsafe_fraction);
+		for (int c = 0; c < 4; c++) {
+			const PhysicsServer3D::MotionCollision &mc = mr.collisions[c];
+			auto it = rid_index.find(mc.collider);
+			res.push_back(c < mr.collision_count && it != rid_index.end() ? (float)it->second : -1.f);
+			put3(res, mc.position);
+			put3(res, mc.normal);
+			res.push_back(mc.depth);
+			put3(res, mc.collider_velocity);
+		}
+		n++;
+	}
+	if (n) {
+		d.arr("motion_queries", step, "f4", { n, 19 }, q.data(), q.size() * 4);
+		d.arr("motion_results", step, "f4", { n, 11 + 4 * 11 }, res.data(), res.size() * 4);
+	}
+}
+
 static void dump_meshes(Dump &d, World &w) {
 	// convex hull meshes as the reference built them (ConvexHullComputer, bradot_shape_3d.cpp:1099)
 	for (size_t i = 0; i < w.shapes.size(); i++) {
@@ -728,6 +786,7 @@ int main(int argc, char **argv) {
 	int steps = 1, dump_from = 0, dump_every = 1, threads = -1, warmup = 0;
 	const char *dump_path = nullptr, *rays_path = nullptr, *state_path = nullptr, *events_path = nullptr;
 	bool slim = false;
+	bool motions = false; // --motions: body_test_motion requests on every dumped step (dump_motions)
 	std::set<int> dump_steps;
 	for (int i = 2; i < argc; i++) {
 		std::string a = argv[i];
@@ -749,6 +808,8 @@ int main(int argc, char **argv) {
 			state_path = argv[++i];
 		} else if (a == "--events") {
 			events_path = argv[++i];
+		} else if (a == "--motions") {
+			motions = true;
 		} else if (a == "--slim") {
 			slim = true;
 		} else if (a == "--dump-steps") { // comma-separated step numbers: dump exactly these (overrides --dump-from / --dump-every)
@@ -1105,6 +1166,9 @@ int main(int argc, char **argv) {
 		if (d.f && dump_this) {
 			dump_step(d, w, s);
 			dump_rays(d, w, s, rays);
+			if (motions) {
+				dump_motions(d, w, s);
+			}
 		}
 	}
 	auto t1 = std::chrono::steady_clock::now();

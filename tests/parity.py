@@ -32,7 +32,7 @@ def write_events(path, events):
         f.write(ev.tobytes())
 
 
-def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays=None, state=None, events=None, warmup=0, slim=False, dump_steps=None):
+def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays=None, state=None, events=None, warmup=0, slim=False, dump_steps=None, motions=False):
     """Step `sc` with the reference; returns (timing dict, dump dict).  `rays` (n, 6) float32 from/to: every dumped step
     also holds ("rays", step) = the reference's intersect_ray answers in space 0.  `state` (n_bodies, 18): transforms and
     velocities given to the moving bodies before the first step.  `events`: (step, body, kind, values) records applied before
@@ -67,6 +67,8 @@ def run_oracle(sc, steps, dump_from=0, dump_every=1, threads=-1, keep=None, rays
         cmd += ["--warmup", str(warmup)]
     if slim:
         cmd += ["--slim"]
+    if motions:
+        cmd += ["--motions"]
     if dump_steps is not None:
         cmd += ["--dump-steps", ",".join(str(int(x)) for x in sorted(set(dump_steps)))]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=3000)

@@ -54,6 +54,18 @@ def test_engine_module_matches_direct_c_abi(tmp_path):
         assert int(casts[i, 3]) == (rest["body"][0] if rest["hit"][0] else -1), i
         if rest["hit"][0]:
             assert np.array_equal(casts[i, 4:7].astype(np.float32), rest["point"][0])
+    # body_test_motion through the RID API == bpc_bodies_test_motion on the same state
+    mot = np.array(out["motions"], np.float64)
+    prm = np.zeros(n, server.MOTION_PARAMS_DT)
+    prm["body"] = np.arange(n)
+    prm["from"] = ps.bodies_read_state()[:n, 0:12]
+    prm["motion"], prm["margin"], prm["max_collisions"] = (0.05, -0.4, 0.0), 0.02, 4
+    mr = ps.bodies_test_motion(prm)
+    assert np.array_equal(mot[:, 0] != 0, mr["collided"] != 0) and mr["collided"].any()
+    hitm = mr["collided"] != 0
+    assert np.array_equal(mot[hitm, 1].astype(np.int32), mr["collisions"][hitm, 0]["collider"])
+    assert np.array_equal(mot[hitm, 2].astype(np.int32), mr["collision_count"][hitm])
+    assert np.array_equal(mot[:, 3].astype(np.float32), mr["collision_safe_fraction"]) and np.array_equal(mot[:, 4:6].astype(np.float32), mr["travel"][:, 0:2])
     ps.finish()
     assert n == min(16, len(sc.bodies)) and hit.all() and np.array_equal(eng_rays[:, 0] != 0, hit)
     assert np.array_equal(eng_rays[:, 1].astype(np.int64), body.astype(np.int64))

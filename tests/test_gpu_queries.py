@@ -275,3 +275,50 @@ def test_query_exclude_lists_against_the_reference():
     hit, body, _, _ = ps.intersect_rays(rays)
     assert np.array_equal(hit, first_r[:, 0] > 0) or (hit != (first_r[:, 0] > 0)).sum() <= 1       # the list is cleared again
     ps.finish()
+
+
+def test_body_test_motion_against_the_reference():
+    """body_test_motion (bradot_space_3d.cpp:651-1029: recovery, cast, rest contacts) for every third body of a settled pile,
+    each from where it stands -- touching its neighbours, so the recovery step has work -- with margins 0.001 / 0.04, 1 or 4
+    collisions asked, recovery_as_collision on a third.  The requests are the harness's (dump "motion_queries").  Collided or
+    not agrees; the safe / unsafe fractions are equal except where a distance test sits within GJK's accuracy of touching.  Most
+    answers are equal to the last bit (median and 90th percentile of every difference: 0); the recovery is a sequential
+    projection over the contacts in tree order, which differs between the two trees, so a body wedged between several
+    neighbours can come out a few millimetres apart (travel: 95 % within 5 mm, all within 5 cm) and then name another
+    neighbour as its deepest contact."""
+    parity_needed()
+    for sc, steps in ((scenes.mixed_pile(5, half=3.5), 60), (scenes.convex_pile(4), 60)):
+        _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1, motions=True)
+        ps = parity.new_server(sc, dump)
+        total = hits = 0
+        for k in (20, 40, 59):
+            parity.load_state(ps, dump, k)
+            q, ref = dump[("motion_queries", k)], dump[("motion_results", k)]
+            prm = np.zeros(len(q), server.MOTION_PARAMS_DT)
+            prm["body"], prm["from"], prm["motion"] = q[:, 0].astype(np.int32), q[:, 1:13], q[:, 13:16]
+            prm["margin"], prm["max_collisions"], prm["flags"] = q[:, 16], q[:, 17].astype(np.int32), q[:, 18].astype(np.uint32)
+            out = ps.bodies_test_motion(prm)
+            same = (out["collided"] > 0) == (ref[:, 0] > 0)
+            assert same.mean() > 0.98, (k, int((~same).sum()))
+            both = same & (ref[:, 0] > 0)
+            exact = (out["collision_safe_fraction"] == ref[:, 9]) & (out["collision_unsafe_fraction"] == ref[:, 10])
+            assert exact[same].mean() > 0.9, (k, int((~exact[same]).sum()))
+            ok = same & exact
+            dtravel = np.abs(out["travel"] - ref[:, 2:5]).max(axis=1)
+            assert np.percentile(dtravel[ok], 50) == 0 and np.percentile(dtravel[ok], 95) < 5e-3 and dtravel[ok].max() < 5e-2, (k, dtravel[ok].max())
+            sel = np.nonzero(ok & both)[0]
+            coll = out["collisions"][sel, 0]
+            agree = coll["collider"] == ref[sel, 11].astype(np.int32)
+            assert agree.mean() > 0.9, (k, int((~agree).sum()))
+            s2 = sel[agree]
+            c2 = out["collisions"][s2, 0]
+            dpos = np.abs(c2["position"] - ref[s2, 12:15]).max(axis=1)
+            dnrm = np.abs(c2["normal"] - ref[s2, 15:18]).max(axis=1)
+            assert np.percentile(dpos, 50) == 0 and np.percentile(dpos, 95) < 3e-3 and np.percentile(dnrm, 95) < 3e-3, (k, np.percentile(dpos, 95), np.percentile(dnrm, 95))
+            assert np.percentile(np.abs(out["collision_depth"][s2] - ref[s2, 8]), 95) < 2e-3
+            many = s2[(ref[s2, 1] > 1)]
+            assert len(many) == 0 or np.mean(out["collision_count"][many] == ref[many, 1].astype(np.int32)) >= 0.8
+            total += len(q)
+            hits += len(sel)
+        assert total > 60 and hits > 30, (total, hits)
+        ps.finish()
