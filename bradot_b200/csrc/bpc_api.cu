@@ -291,6 +291,157 @@ extern "C" int bpc_shape_create_convex(bpc_context *ctx, const float *verts, int
     return (int)ctx->h_shapes.size() - 1;
 }
 
+
+// ---- static triangle meshes (ConcavePolygonShape3D): BradotConcavePolygonShape3D::_setup (P3D/bradot_shape_3d.cpp:1505-1672)
+namespace {
+struct CvElem {
+    V3 mn, mx, center;
+    int face;
+};
+struct CvNode {
+    V3 pos, size;
+    int left, right, face;
+};
+// _volume_build_bvh + _fill_bvh in one: median split along the longest axis of the elements' box, nodes in pre-order (the left
+// child of node i is i + 1).  The reference sorts with its own introsort; elements whose centres tie on the split axis may come
+// out in another order here (std::stable_sort) -- same tree quality, possibly another order of faces inside a leaf pair.
+int cv_build(std::vector<CvElem> &e, int lo, int n, std::vector<CvNode> &out) {
+    int idx = (int)out.size();
+    out.push_back(CvNode());
+    if (n == 1) {
+        out[idx].pos = e[lo].mn;
+        out[idx].size = e[lo].mx - e[lo].mn;
+        out[idx].left = out[idx].right = -1;
+        out[idx].face = e[lo].face;
+        return idx;
+    }
+    V3 mn = e[lo].mn, mx = e[lo].mx;
+    for (int i = 1; i < n; i++) {
+        for (int k = 0; k < 3; k++) {
+            mn[k] = std::min(mn[k], e[lo + i].mn[k]);
+            mx[k] = std::max(mx[k], e[lo + i].mx[k]);
+        }
+    }
+    V3 size = mx - mn;
+    int axis = 0; // AABB::get_longest_axis_index: x unless y or z is strictly longer
+    float max_size = size.x;
+    if (size.y > max_size) {
+        axis = 1;
+        max_size = size.y;
+    }
+    if (size.z > max_size) axis = 2;
+    std::stable_sort(e.begin() + lo, e.begin() + lo + n, [axis](const CvElem &a, const CvElem &b) { return a.center[axis] < b.center[axis]; });
+    int split = n / 2;
+    out[idx].pos = mn;
+    out[idx].size = size;
+    out[idx].face = -1;
+    int l = cv_build(e, lo, split, out);
+    int r = cv_build(e, lo + split, n - split, out);
+    out[idx].left = l;
+    out[idx].right = r;
+    return idx;
+}
+} // namespace
+
+extern "C" int bpc_shape_create_concave(bpc_context *ctx, const float *faces, int n_faces, int backface_collision, const float *bvh_nodes, int n_nodes,
+                                        const float *normals) {
+    if (!ctx) return -1;
+    if (n_faces <= 0 || !faces) return fail(ctx, "bpc_shape_create_concave: empty mesh");
+    if ((bvh_nodes != nullptr) != (n_nodes > 0)) return fail(ctx, "bpc_shape_create_concave: a tree needs its node count");
+    std::vector<CvNode> nodes;
+    if (bvh_nodes) { // a tree handed over (the reference's own, in tests): validate, keep
+        for (int i = 0; i < n_nodes; i++) {
+            const float *f = bvh_nodes + 9 * i;
+            CvNode nd;
+            nd.pos = V3(f[0], f[1], f[2]);
+            nd.size = V3(f[3], f[4], f[5]);
+            nd.left = (int)f[6];
+            nd.right = (int)f[7];
+            nd.face = (int)f[8];
+            if (nd.face >= n_faces || (nd.face < 0 && (nd.left != i + 1 || nd.right <= i + 1 || nd.right >= n_nodes)))
+                return fail(ctx, "bpc_shape_create_concave: the tree is not a pre-order tree over the faces");
+            nodes.push_back(nd);
+        }
+    } else {
+        std::vector<CvElem> el(n_faces);
+        for (int i = 0; i < n_faces; i++) {
+            V3 mn, mx;
+            for (int v = 0; v < 3; v++) {
+                V3 p(faces[9 * i + 3 * v], faces[9 * i + 3 * v + 1], faces[9 * i + 3 * v + 2]);
+                if (v == 0) {
+                    mn = mx = p;
+                } else {
+                    for (int k = 0; k < 3; k++) {
+                        mn[k] = std::min(mn[k], p[k]);
+                        mx[k] = std::max(mx[k], p[k]);
+                    }
+                }
+            }
+            el[i].mn = mn;
+            el[i].mx = mx;
+            el[i].center = mn + (mx - mn) * 0.5f; // AABB::get_center
+            el[i].face = i;
+        }
+        nodes.reserve(2 * (size_t)n_faces);
+        cv_build(el, 0, n_faces, nodes);
+    }
+    MeshRec m;
+    memset(&m, 0, sizeof(m));
+    m.vert_ofs = (uint32_t)ctx->h_mverts.size();
+    m.vert_cnt = (uint32_t)n_faces * 3u;
+    m.face_ofs = (uint32_t)ctx->h_mplanes.size();
+    m.face_cnt = (uint32_t)nodes.size();
+    m.edge_ofs = (uint32_t)ctx->h_medges.size();
+    m.edge_cnt = backface_collision ? 1u : 0u;
+    m.index_ofs = (uint32_t)ctx->h_mindex.size();
+    m.scan_all = 2; // marks a triangle mesh
+    V3 mn, mx;
+    for (int i = 0; i < n_faces * 3; i++) {
+        V3 v(faces[3 * i], faces[3 * i + 1], faces[3 * i + 2]);
+        ctx->h_mverts.push_back(make_float4(v.x, v.y, v.z, 0.f));
+        if (i == 0) {
+            mn = mx = v;
+        } else {
+            for (int k = 0; k < 3; k++) {
+                mn[k] = std::min(mn[k], v[k]);
+                mx[k] = std::max(mx[k], v[k]);
+            }
+        }
+    }
+    for (const CvNode &nd : nodes) {
+        float fi, ri;
+        int32_t face = nd.face, right = nd.right;
+        memcpy(&fi, &face, 4);
+        memcpy(&ri, &right, 4);
+        ctx->h_mplanes.push_back(make_float4(nd.pos.x, nd.pos.y, nd.pos.z, fi));
+        ctx->h_mplanes.push_back(make_float4(nd.size.x, nd.size.y, nd.size.z, ri));
+        // (h_mfaces runs parallel to h_mplanes -- a hull's face_ofs indexes both: keep them the same length)
+        ctx->h_mfaces.push_back(make_uint2(0u, 0u));
+        ctx->h_mfaces.push_back(make_uint2(0u, 0u));
+    }
+    for (int i = 0; i < n_faces; i++) {
+        V3 n;
+        if (normals) {
+            n = V3(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]);
+        } else { // Face3::get_plane -> Plane(v0, v1, v2, CLOCKWISE): (v0 - v2) x (v0 - v1), normalised (core/math/plane.cpp:37-46)
+            V3 a(faces[9 * i], faces[9 * i + 1], faces[9 * i + 2]), b(faces[9 * i + 3], faces[9 * i + 4], faces[9 * i + 5]),
+                    c(faces[9 * i + 6], faces[9 * i + 7], faces[9 * i + 8]);
+            n = normalized(cross(a - c, a - b));
+        }
+        ctx->h_mplanes.push_back(make_float4(n.x, n.y, n.z, 0.f));
+        ctx->h_mfaces.push_back(make_uint2(0u, 0u));
+    }
+    ShapeRec r;
+    memset(&r, 0, sizeof(r));
+    r.meta = make_uint4(SH_CONCAVE, (uint32_t)ctx->h_meshes.size(), 0, 0);
+    r.aabb_pos = make_float4(mn.x, mn.y, mn.z, 0.f);
+    r.aabb_size = make_float4(mx.x - mn.x, mx.y - mn.y, mx.z - mn.z, 0.f);
+    ctx->h_meshes.push_back(m);
+    ctx->h_shapes.push_back(r);
+    ctx->shapes_dirty = true;
+    return (int)ctx->h_shapes.size() - 1;
+}
+
 template <typename T>
 static int upload(bpc_context *ctx, DevBuf<T> &d, const std::vector<T> &h) {
     if (h.empty()) return 0;

@@ -44,7 +44,7 @@ __device__ __forceinline__ Sh ar_shape(const ArArgs &a, uint32_t type, float4 p)
     s.type = type;
     s.p = p;
     s.m.nv = s.m.nf = s.m.ne = 0;
-    if (type == SH_CONVEX) {
+    if (type == SH_CONVEX || type == SH_CONCAVE) {
         MeshRec m = a.meshes[__float_as_uint(p.x)];
         s.m.verts = a.mverts + m.vert_ofs;
         s.m.planes = a.mplanes + m.face_ofs;
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(128) k_area_pairs(ArArgs a) {
             Sh sa = ar_shape(a, ar.shape_type, ar.shape_p);
             X3 xa(M3(f4v(ar.s0), f4v(ar.s1), f4v(ar.s2)), f4v(ar.so));
             Manifold *none = nullptr;
-            result = solve_static<true>(sb, xb, sa, xa, *none, nullptr);
+            result = solve_static<true, false, true>(sb, xb, sa, xa, *none, nullptr);
         }
         uint32_t at = cnt;
         for (uint32_t q = 0; q < cnt; q++) {
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(64) k_area_area(ArArgs a, uint32_t n, const ui
     Sh sa = ar_shape(a, ra.shape_type, ra.shape_p), sb = ar_shape(a, rb.shape_type, rb.shape_p);
     X3 xa(M3(f4v(ra.s0), f4v(ra.s1), f4v(ra.s2)), f4v(ra.so)), xb(M3(f4v(rb.s0), f4v(rb.s1), f4v(rb.s2)), f4v(rb.so));
     Manifold *none = nullptr;
-    result[t] = solve_static<true>(sa, xa, sb, xb, *none, nullptr) ? 1u : 0u;
+    result[t] = solve_static<true, false, true>(sa, xa, sb, xb, *none, nullptr) ? 1u : 0u;
 }
 
 __global__ void k_area_clear_moved(uint32_t n, AreaRec *areas) {
@@ -198,7 +198,7 @@ static int area_from_desc(bpc_context *ctx, const bpc_area_desc &d, AreaRec &r) 
     r.s2 = make_float4(s[6], s[7], s[8], 0.f);
     r.so = make_float4(s[9], s[10], s[11], 0.f);
     r.shape_p = sh.p;
-    if (sh.meta.x == SH_CONVEX) memcpy(&r.shape_p.x, &sh.meta.y, 4);
+    if (sh.meta.x == SH_CONVEX || sh.meta.x == SH_CONCAVE) memcpy(&r.shape_p.x, &sh.meta.y, 4);
     r.shape_type = sh.meta.x;
     r.space = (uint32_t)d.space;
     r.layer = d.layer;

@@ -47,7 +47,7 @@ __device__ __forceinline__ Sh load_shape(const NpArgs &a, uint32_t sid) {
     s.type = r.meta.x;
     s.p = r.p;
     s.m.nv = s.m.nf = s.m.ne = 0;
-    if (s.type == SH_CONVEX) {
+    if (s.type == SH_CONVEX || s.type == SH_CONCAVE) {
         MeshRec m = a.meshes[r.meta.y];
         s.m.verts = a.mverts + m.vert_ofs;
         s.m.planes = a.mplanes + m.face_ofs;
@@ -69,7 +69,7 @@ __device__ __forceinline__ Sh load_shape_fast(const NpArgs &a, uint32_t body, ui
     s.type = meta_x >> 24;
     s.p = a.shape_p[body];
     s.m.nv = s.m.nf = s.m.ne = 0;
-    if (s.type == SH_CONVEX) {
+    if (s.type == SH_CONVEX || s.type == SH_CONCAVE) {
         MeshRec m = a.meshes[__float_as_uint(s.p.x)];
         s.m.verts = a.mverts + m.vert_ofs;
         s.m.planes = a.mplanes + m.face_ofs;
@@ -107,6 +107,7 @@ __device__ __forceinline__ uint32_t kept_colour(uint32_t old_bits, uint32_t new_
     return ((new_bits & 0x100u) && ((old_bits ^ new_bits) & 0x600u) == 0u) ? (old_bits & PAIR_COLOUR_MASK) : 0u;
 }
 
+template <bool MESH>
 __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     bool work = false, cwork = false;
@@ -160,7 +161,7 @@ __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
                     cwork = !cw_quick_separated(sa, xA, sb, xB, sep_axis);
                 } else {
                     Manifold *none = nullptr;
-                    work = solve_static<true>(sa, xA, sb, xB, *none, &sep_axis);
+                    work = solve_static<true, false, MESH>(sa, xA, sb, xB, *none, &sep_axis);
                 }
             }
             if (!work && !cwork) {
@@ -189,6 +190,7 @@ __global__ void __launch_bounds__(128) k_pair_test(NpArgs a) {
     }
 }
 
+template <bool MESH>
 __global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
     uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= a.counters[CNT_WORK]) return;
@@ -230,7 +232,7 @@ __global__ void __launch_bounds__(NP_THREADS) k_pair_setup(NpArgs a) {
     Sh sa = load_shape_fast(a, ia, ma.x);
     Sh sb = load_shape_fast(a, ib, mb.x);
     V3 sep_axis = f4v(h.sep);
-    bool collided = solve_static<false>(sa, xA, sb, xB, m, &sep_axis);
+    bool collided = solve_static<false, false, MESH>(sa, xA, sb, xB, m, &sep_axis);
     for (int c = 0; c < m.count; c++) {
         ContactGeo g;
         g.la = v4(m.la[c], __uint_as_float(m.used[c] ? 1u : 0u));
@@ -399,9 +401,13 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
         if (bpc_radix_sort(ctx, &ctx->keys.p, &ctx->keys_alt.p, &ctx->vals.p, &ctx->vals_alt.p, n, 0xffull)) return -1;
         a.perm = ctx->vals.p;
     }
-    k_pair_test<<<(n + 127) / 128, 128, 0, ctx->stream>>>(a);
+    // (scenes without a triangle mesh run the instances compiled without that branch: same code as before meshes existed)
+    const bool mesh = (ctx->shape_type_mask >> SH_CONCAVE) & 1u;
+    if (mesh) k_pair_test<true><<<(n + 127) / 128, 128, 0, ctx->stream>>>(a);
+    else k_pair_test<false><<<(n + 127) / 128, 128, 0, ctx->stream>>>(a);
     // the survivor count stays on the device: launch for the worst case, surplus threads exit at once
-    k_pair_setup<<<(n + NP_THREADS - 1) / NP_THREADS, NP_THREADS, 0, ctx->stream>>>(a);
+    if (mesh) k_pair_setup<true><<<(n + NP_THREADS - 1) / NP_THREADS, NP_THREADS, 0, ctx->stream>>>(a);
+    else k_pair_setup<false><<<(n + NP_THREADS - 1) / NP_THREADS, NP_THREADS, 0, ctx->stream>>>(a);
     ctx->launches += 2;
     if (hulls) {
         k_convex_warp<<<(n + CW_WARPS - 1) / CW_WARPS, CW_WARPS * 32, 0, ctx->stream>>>(a);

@@ -51,7 +51,7 @@ __device__ __forceinline__ Sh qs_shape(const QsArgs &a, uint32_t type, float4 p)
     s.type = type;
     s.p = p;
     s.m.nv = s.m.nf = s.m.ne = 0;
-    if (type == SH_CONVEX) {
+    if (type == SH_CONVEX || type == SH_CONCAVE) {
         MeshRec m = a.meshes[__float_as_uint(p.x)];
         s.m.verts = a.mverts + m.vert_ofs;
         s.m.planes = a.mplanes + m.face_ofs;
@@ -79,8 +79,8 @@ __device__ inline void qs_candidate(const QsArgs &a, uint32_t j, const Sh &qs, c
     Sh sb = qs_shape(a, m.x >> 24, a.shape_p[j]);
     Manifold *none = nullptr;
     // (ShapeParameters::margin grows the query shape: the withMargin routines, bradot_space_3d.cpp:241)
-    bool hit = a.margin != 0.f ? solve_static<true, true>(qs, qx, sb, xb, *none, nullptr, nullptr, nullptr, a.margin, 0.f)
-                               : solve_static<true>(qs, qx, sb, xb, *none, nullptr);
+    bool hit = a.margin != 0.f ? solve_static<true, true, true>(qs, qx, sb, xb, *none, nullptr, nullptr, nullptr, a.margin, 0.f)
+                               : solve_static<true, false, true>(qs, qx, sb, xb, *none, nullptr);
     if (!hit) return;
     a.bodies[(size_t)r * a.max_results + cc] = (int32_t)j;
     cc++;
@@ -128,7 +128,7 @@ __device__ inline void qs_for_candidates(const QsArgs &a, V3 qmin, V3 qmax, F f)
 __device__ inline void qs_request(const QsArgs &a, uint32_t r, float grow, Sh &qs, X3 &qx, V3 &qmin, V3 &qmax) {
     const ShapeRec sr = a.shapes[a.shape_ids[r]];
     float4 p = sr.p;
-    if (sr.meta.x == SH_CONVEX) p.x = __uint_as_float(sr.meta.y);
+    if (sr.meta.x == SH_CONVEX || sr.meta.x == SH_CONCAVE) p.x = __uint_as_float(sr.meta.y);
     qs = qs_shape(a, sr.meta.x, p);
     const float *f = a.xforms + (size_t)r * 12;
     qx = X3(M3(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8])), V3(f[9], f[10], f[11]));
@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_rest_info(QsArgs a) {
         if (!qs_body(a, j, sb, xb)) return;
         sink.cur_body = j;
         Manifold *none = nullptr;
-        solve_static<false, true>(qs, qx, sb, xb, *none, nullptr, nullptr, &sink, margin, 0.f);
+        solve_static<false, true, true>(qs, qx, sb, xb, *none, nullptr, nullptr, &sink, margin, 0.f);
     });
     bpc_rest_info o;
     memset(&o, 0, sizeof(o));
@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
     if (r >= a.n) return;
     const ShapeRec sr = a.shapes[a.shape_ids[r]];
     float4 p = sr.p;
-    if (sr.meta.x == SH_CONVEX) p.x = __uint_as_float(sr.meta.y);
+    if (sr.meta.x == SH_CONVEX || sr.meta.x == SH_CONCAVE) p.x = __uint_as_float(sr.meta.y);
     Sh qs = qs_shape(a, sr.meta.x, p);
     const float *f = a.xforms + (size_t)r * 12;
     X3 qx(M3(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8])), V3(f[9], f[10], f[11]));
@@ -359,8 +359,8 @@ __device__ inline void qc_candidate(const QsArgs &a, uint32_t j, const Sh &qs, c
     }
     Sh sb = qs_shape(a, m.x >> 24, a.shape_p[j]);
     Manifold *none = nullptr;
-    if (a.margin != 0.f) solve_static<false, true>(qs, qx, sb, xb, *none, nullptr, &sink, nullptr, a.margin, 0.f); // (:419)
-    else solve_static<false>(qs, qx, sb, xb, *none, nullptr, &sink);
+    if (a.margin != 0.f) solve_static<false, true, true>(qs, qx, sb, xb, *none, nullptr, &sink, nullptr, a.margin, 0.f); // (:419)
+    else solve_static<false, false, true>(qs, qx, sb, xb, *none, nullptr, &sink);
 }
 
 __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
     if (r >= a.n) return;
     const ShapeRec sr = a.shapes[a.shape_ids[r]];
     float4 p = sr.p;
-    if (sr.meta.x == SH_CONVEX) p.x = __uint_as_float(sr.meta.y);
+    if (sr.meta.x == SH_CONVEX || sr.meta.x == SH_CONCAVE) p.x = __uint_as_float(sr.meta.y);
     Sh qs = qs_shape(a, sr.meta.x, p);
     const float *f = a.xforms + (size_t)r * 12;
     X3 qx(M3(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8])), V3(f[9], f[10], f[11]));
@@ -737,7 +737,7 @@ __device__ __noinline__ void mt_rest_contacts(const MtArgs *m, const QsArgs *a, 
         if (!mt_body(*m, self, self_mask, j, sb, xb)) return;
         rcd->cur_body = j;
         Manifold *none = nullptr;
-        solve_static<false, true>(*bs, *bsx, sb, xb, *none, nullptr, nullptr, rcd, margin, 0.f);
+        solve_static<false, true, true>(*bs, *bsx, sb, xb, *none, nullptr, nullptr, rcd, margin, 0.f);
     });
 }
 
@@ -751,7 +751,7 @@ __device__ __noinline__ void mt_recover_contacts(const MtArgs *m, const QsArgs *
         X3 xb;
         if (!mt_body(*m, self, self_mask, j, sb, xb)) return;
         Manifold *none = nullptr;
-        solve_static<false, true>(*bs, *bsx, sb, xb, *none, nullptr, sink, nullptr, margin, 0.f);
+        solve_static<false, true, true>(*bs, *bsx, sb, xb, *none, nullptr, sink, nullptr, margin, 0.f);
     });
 }
 

@@ -509,8 +509,11 @@ __device__ inline bool col_plane(const Sh &pl_shape, const X3 &xp, const Sh &b, 
     return found;
 }
 
+#include "np_face.cuh"
+
 // BradotCollisionSolver3D::solve_static (…collision_solver_3d.cpp:362-435) + sat_calculate_penetration dispatch (…sat.cpp:2296-2421)
-template <bool TEST, bool MG = false>
+// MESH = triangle meshes may take part (kernels of scenes without one are compiled without that branch)
+template <bool TEST, bool MG = false, bool MESH = false>
 __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, const X3 &xb, Manifold &m, V3 *sep_axis, RawSink *raw = nullptr,
                                     RestSink *rest = nullptr, float margin_A = 0.f, float margin_B = 0.f) {
     Collector c;
@@ -526,6 +529,15 @@ __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, co
         if (ta == SH_PLANE && tb == SH_PLANE) return false;
         if (ta > tb) return col_plane<TEST, MG>(sb, xb, sa, xa, c, true, margin_A);
         return col_plane<TEST, MG>(sa, xa, sb, xb, c, false, margin_B);
+    }
+    if (MESH && max(ta, tb) == SH_CONCAVE) { // a static triangle mesh: the other shape against every face its box meets
+        if (ta == SH_CONCAVE && tb == SH_CONCAVE) return false;
+        if (MG) {
+            c.margin_A = margin_A; // (solve_concave hands both margins on unswapped, ...collision_solver_3d.cpp:425-429)
+            c.margin_B = margin_B;
+        }
+        if (ta > tb) return solve_concave<TEST, MG>(sb, xb, sa, xa, c, true, margin_A);
+        return solve_concave<TEST, MG>(sa, xa, sb, xb, c, false, margin_A);
     }
     // ordered by shape type; swapped BY VALUE: pointers to whichever of two locals would pin all four in local memory
     const bool swap = ta > tb;

@@ -14,7 +14,7 @@ import struct
 
 import numpy as np
 
-SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONVEX = range(7)
+SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONVEX, SHAPE_CONCAVE = range(8)
 MODE_STATIC, MODE_KINEMATIC, MODE_RIGID, MODE_RIGID_LINEAR = range(4)
 JOINT_PIN, JOINT_HINGE = 0, 1
 
@@ -728,3 +728,57 @@ def area_zones_script():
     add(90, 16, 7)                            # the tube is freed inside 12: 12 and the well hear it leave
     add(100, 12, 6, place(50.0, 20.0, 0.0))   # 12 itself moves off: it leaves the well
     return ev
+
+
+def terrain_faces(n=12, size=8.0, height=0.6, seed=3):
+    """A bumpy square of 2 n^2 triangles (vertices jittered so that no two triangle centres tie on an axis), facing up."""
+    rng = np.random.default_rng(seed)
+    xs = np.linspace(-size / 2, size / 2, n + 1)
+    gx, gz = np.meshgrid(xs, xs, indexing="ij")
+    gx = gx + rng.uniform(-0.05, 0.05, gx.shape)
+    gz = gz + rng.uniform(-0.05, 0.05, gz.shape)
+    gy = height * (np.sin(gx * 0.9) * np.cos(gz * 0.7) + 0.3 * rng.uniform(-1, 1, gx.shape))
+    p = np.stack([gx, gy, gz], -1).astype(np.float32)
+    faces = []
+    for i in range(n):
+        for j in range(n):
+            a, b, c, d = p[i, j], p[i + 1, j], p[i + 1, j + 1], p[i, j + 1]
+            faces.append((a, b, c))        # winding: the reference's face normal (v0 - v2) x (v0 - v1) points up, the solid side is below
+            faces.append((a, c, d))
+    return np.array(faces, np.float32).reshape(-1, 3, 3)
+
+
+def terrain_pile(n=5, seed=11, backface=False):
+    """Static concave colliders: spheres, boxes, capsules and hulls dropped onto a bumpy triangle mesh with a
+    second, tilted mesh (a ramp made of two big triangles) above one corner; world boundaries far below catch what falls off."""
+    sc = Scene(name="terrain_pile")
+    sc.add_static_plane((0, 1, 0), -6.0)
+    tf = terrain_faces()
+    terrain = sc.add_shape(SHAPE_CONCAVE, (1.0 if backface else 0.0,), verts=tf.reshape(-1, 3))
+    ramp_faces = np.array([[(-1.5, 0, -1.5), (1.5, 0, 1.5), (1.5, 0, -1.5)], [(-1.5, 0, -1.5), (-1.5, 0, 1.5), (1.5, 0, 1.5)]], np.float32)
+    ramp = sc.add_shape(SHAPE_CONCAVE, (1.0,), verts=ramp_faces.reshape(-1, 3))
+    sc.add_bodies(1, mode=MODE_STATIC, shape=terrain)
+    x = IDENT12.copy()
+    c, s = np.cos(0.35), np.sin(0.35)
+    x[0], x[1], x[3], x[4] = c, -s, s, c          # tilted about z
+    x[9], x[10], x[11] = 2.0, 2.2, 2.0
+    sc.add_bodies(1, mode=MODE_STATIC, shape=ramp, xf=x)
+    rng = np.random.default_rng(seed)
+    hulls = [sc.add_shape(SHAPE_CONVEX, verts=rng.normal(size=(14, 3)) * 0.22) for _ in range(3)]
+    g = np.stack(np.meshgrid(np.arange(n), np.arange(n), indexing="ij"), -1).reshape(-1, 2)
+    for k, (i, j) in enumerate(g):
+        kind = k % 4
+        if kind == 0:
+            sh = sc.add_shape(SHAPE_SPHERE, (rng.uniform(0.18, 0.3),))
+        elif kind == 1:
+            sh = sc.add_shape(SHAPE_BOX, tuple(rng.uniform(0.15, 0.3, 3)))
+        elif kind == 2:
+            sh = sc.add_shape(SHAPE_CAPSULE, (rng.uniform(0.12, 0.2), rng.uniform(0.6, 0.9)))
+        else:
+            sh = hulls[k % 3]
+        f = IDENT12.copy()
+        ang = rng.uniform(0, 6.28)
+        f[0], f[2], f[6], f[8] = np.cos(ang), np.sin(ang), -np.sin(ang), np.cos(ang)
+        f[9], f[10], f[11] = (i - (n - 1) / 2) * 1.3 + rng.uniform(-0.1, 0.1), 2.0 + 0.9 * (k % 3) + (2.5 if (i >= n - 2 and j >= n - 2) else 0.0), (j - (n - 1) / 2) * 1.3 + rng.uniform(-0.1, 0.1)
+        sc.add_bodies(1, shape=sh, xf=f, angvel=tuple(rng.uniform(-1, 1, 3)), mass=1.0)
+    return sc

@@ -37,7 +37,7 @@ _STATE_WIDTH = {0: 12, 1: 3, 2: 3, 3: 1, 4: 1}
 
 EXPORTS = [
     "bpc_create", "bpc_destroy", "bpc_last_error", "bpc_set_stream", "bpc_space_create", "bpc_space_set_param",
-    "bpc_shape_create", "bpc_shape_create_convex", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
+    "bpc_shape_create", "bpc_shape_create_convex", "bpc_shape_create_concave", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
     "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
     "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
@@ -89,6 +89,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_space_set_param.argtypes = [vp, ci, ci, cf]
     lib.bpc_shape_create.argtypes = [vp, ci, vp]
     lib.bpc_shape_create_convex.argtypes = [vp, vp, ci, vp, vp, ci, vp, ci, vp, ci]
+    lib.bpc_shape_create_concave.argtypes = [vp, vp, ci, ci, vp, ci, vp]
     lib.bpc_bodies_create.argtypes = [vp, vp, ci]
     lib.bpc_bodies_write.argtypes = [vp, ci, ci, ci, vp]
     lib.bpc_bodies_read.argtypes = [vp, ci, ci, ci, vp]
@@ -214,6 +215,14 @@ class PhysicsServerCUDA:
         ed = np.ascontiguousarray(mesh["edges"], np.int32)
         return self._check(self.lib.bpc_shape_create_convex(self.ctx, _ptr(v), len(v), _ptr(pl), _ptr(fa), len(fa), _ptr(ix), len(ix),
                                                             _ptr(ed), len(ed)))
+
+    def concave_polygon_shape_create(self, faces, backface_collision=False, bvh=None, normals=None):
+        """faces (n, 3, 3) or (n, 9) float32; bvh (nodes, 9) + normals (n, 3): a ready tree (the reference's, from a dump)."""
+        f = np.ascontiguousarray(faces, np.float32).reshape(-1, 9)
+        b = None if bvh is None else np.ascontiguousarray(bvh, np.float32).reshape(-1, 9)
+        nr = None if normals is None else np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        return self._check(self.lib.bpc_shape_create_concave(self.ctx, _ptr(f), len(f), 1 if backface_collision else 0, None if b is None else _ptr(b),
+                                                             0 if b is None else len(b), None if nr is None else _ptr(nr)))
 
     # -- bodies -------------------------------------------------------------------------------
     def bodies_create(self, records):
@@ -488,7 +497,11 @@ class PhysicsServerCUDA:
             sp = self.space_create()
             self.space_set_param(sp, SPACE_PARAM_SOLVER_ITERATIONS, sc.iterations + k * getattr(sc, "iter_step", 0))
         for i, s in enumerate(sc.shapes):
-            if s["type"] == scenes.SHAPE_CONVEX:
+            if s["type"] == scenes.SHAPE_CONCAVE:
+                tree = (meshes or {}).get(("concave", i))
+                faces = sc.verts[int(s["vert_ofs"]):int(s["vert_ofs"]) + int(s["vert_cnt"])]
+                self.concave_polygon_shape_create(faces, s["p"][0] != 0, None if tree is None else tree[0], None if tree is None else tree[1])
+            elif s["type"] == scenes.SHAPE_CONVEX:
                 if meshes is None or i not in meshes:
                     from . import hull
                     key = (int(s["vert_ofs"]), int(s["vert_cnt"]))
@@ -520,6 +533,8 @@ def meshes_from_dump(dump):
     """Collect the convex hulls an oracle dump holds (oracle/ref_harness.cpp dump_meshes)."""
     out = {}
     for (name, idx), arr in dump.items():
+        if name == "concave_bvh":
+            out[("concave", idx)] = (arr, dump[("concave_normals", idx)])
         if name == "mesh_verts":
             out[idx] = {"verts": arr, "planes": dump[("mesh_planes", idx)], "faces": dump[("mesh_faces", idx)],
                         "index": dump[("mesh_index", idx)], "edges": dump[("mesh_edges", idx)]}

@@ -126,6 +126,15 @@ int bpc_shape_create(bpc_context *ctx, int type, const float params[4]);
  * (vertex_a, vertex_b, face_a, face_b); planes: per face (nx, ny, nz, d). */
 int bpc_shape_create_convex(bpc_context *ctx, const float *verts, int n_verts, const float *planes, const int32_t *faces, int n_faces,
                             const int32_t *indices, int n_indices, const int32_t *edges, int n_edges);
+/* ConcavePolygonShape3D (static triangle meshes; P3D/bradot_shape_3d.cpp:1289-1690): faces = n_faces x 9 floats
+ * (three vertices each).  Only STATIC bodies may carry one.  The tree over the faces is built here as the reference builds its
+ * own (median split along the longest axis, P3D/bradot_shape_3d.cpp:1541-1586) unless one is handed over: bvh_nodes = n_nodes x 9
+ * floats (box position, box size, left, right, face index or -1) in pre-order, normals = n_faces x 3 -- what the tests do with
+ * the reference's own tree, so that faces are met in its order.  Against a mesh: the step (all four body shapes), intersect_shape,
+ * collide_shape, rest_info, body_test_motion's recovery and rest steps.  Not built: rays and points against a mesh, the GJK
+ * distance to a mesh (cast_motion and the cast of body_test_motion pass through it), HeightMapShape3D. */
+int bpc_shape_create_concave(bpc_context *ctx, const float *faces, int n_faces, int backface_collision, const float *bvh_nodes, int n_nodes,
+                             const float *normals);
 
 /* ---- bodies */
 int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, int n); /* returns first body index */

@@ -723,6 +723,25 @@ static void dump_meshes(Dump &d, World &w) {
 	// convex hull meshes as the reference built them (ConvexHullComputer, bradot_shape_3d.cpp:1099)
 	for (size_t i = 0; i < w.shapes.size(); i++) {
 		BradotShape3D *sh = w.ps->shape_owner.get_or_null(w.shapes[i]);
+		if (sh->get_type() == PhysicsServer3D::SHAPE_CONCAVE_POLYGON) {
+			// the tree over the faces and the face normals as the reference built them (bradot_shape_3d.cpp:1614-1672):
+			// "concave_bvh" (n_nodes, 9) = box position, box size, left, right, face; "concave_normals" (n_faces, 3)
+			BradotConcavePolygonShape3D *cc = static_cast<BradotConcavePolygonShape3D *>(sh);
+			std::vector<float> nodes, normals;
+			for (int k = 0; k < cc->bvh.size(); k++) {
+				put3(nodes, cc->bvh[k].aabb.position);
+				put3(nodes, cc->bvh[k].aabb.size);
+				nodes.push_back((float)cc->bvh[k].left);
+				nodes.push_back((float)cc->bvh[k].right);
+				nodes.push_back((float)cc->bvh[k].face_index);
+			}
+			for (int k = 0; k < cc->faces.size(); k++) {
+				put3(normals, cc->faces[k].normal);
+			}
+			d.arr("concave_bvh", (int)i, "f4", { (uint64_t)cc->bvh.size(), 9 }, nodes.data(), nodes.size() * 4);
+			d.arr("concave_normals", (int)i, "f4", { (uint64_t)cc->faces.size(), 3 }, normals.data(), normals.size() * 4);
+			continue;
+		}
 		if (sh->get_type() != PhysicsServer3D::SHAPE_CONVEX_POLYGON) {
 			continue;
 		}
@@ -914,6 +933,18 @@ int main(int argc, char **argv) {
 					pts.push_back(Vector3(v[0], v[1], v[2]));
 				}
 				ps->shape_set_data(sh, pts);
+			} break;
+			case PhysicsServer3D::SHAPE_CONCAVE_POLYGON: { // vertices: three per face; p[0] != 0: backface_collision
+				sh = ps->concave_polygon_shape_create();
+				Vector<Vector3> pts;
+				for (uint32_t k = 0; k < s.vert_cnt; k++) {
+					const float *v = &sverts[(s.vert_ofs + k) * 3];
+					pts.push_back(Vector3(v[0], v[1], v[2]));
+				}
+				Dictionary dct;
+				dct["faces"] = pts;
+				dct["backface_collision"] = s.p[0] != 0.f;
+				ps->shape_set_data(sh, dct);
 			} break;
 			default:
 				fprintf(stderr, "unsupported shape type %u\n", s.type);
