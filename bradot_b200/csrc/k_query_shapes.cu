@@ -204,6 +204,66 @@ __global__ void __launch_bounds__(QS_THREADS) k_rest_info(QsArgs a) {
     a.rest_out[r] = o;
 }
 
+// BradotCollisionSolver3D::solve_distance with a triangle mesh as shape B (...collision_solver_3d.cpp:528-586): the faces whose
+// boxes meet the caller's hint box (the box of the whole motion, taken into the mesh's space) are tried one by one with the
+// GJK distance (concave_distance_callback, :437-457); the first face touched ends the walk, else the closest pair of points
+// over the faces tried is the answer.
+__device__ inline bool solve_distance_any(const GjkBody &A, const GjkBody &B, V3 hint_min, V3 hint_max, V3 &r_A, V3 &r_B) {
+    if (B.s.type != SH_CONCAVE) return solve_distance(A, B, r_A, r_B);
+    const MeshView &m = B.s.m;
+    r_A = r_B = V3();
+    if (m.nf == 0) return true;
+    V3 hpos = hint_min - B.x.o, hsize = hint_max - hint_min;
+    V3 half(hsize.x * 0.5f, hsize.y * 0.5f, hsize.z * 0.5f);
+    V3 center(hpos.x + half.x, hpos.y + half.y, hpos.z + half.z);
+    V3 lpos, lsize;
+    for (int i = 0; i < 3; i++) {
+        V3 axis = B.x.b.col(i);
+        float axis_scale = 1.0f / length(axis);
+        axis *= axis_scale;
+        // AABB::project_range_in_plane(Plane(axis)) (core/math/aabb.h:375-383)
+        float len = dot(vabs(axis), half);
+        float distance = dot(axis, center);
+        float smin = distance - len, smax = distance + len;
+        smin *= axis_scale;
+        smax *= axis_scale;
+        lpos[i] = smin;
+        lsize[i] = smax - smin;
+    }
+    const float4 *nodes = m.planes;
+    GjkBody F;
+    F.s = B.s;
+    F.x = B.x;
+    F.motion = V3();
+    F.swept = false;
+    F.is_face = true;
+    bool tested = false;
+    int stack[64];
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp) {
+        int idx = stack[--sp];
+        float4 n0 = __ldg(&nodes[2 * idx]), n1 = __ldg(&nodes[2 * idx + 1]);
+        if (!aabb_intersects(lpos, lsize, f4v(n0), f4v(n1))) continue;
+        int face_index = __float_as_int(n0.w);
+        if (face_index >= 0) {
+            for (int v = 0; v < 3; v++) F.fv[v] = mv_vert(m, 3 * face_index + v);
+            V3 cA, cB;
+            if (!gjk_distance(A, F, cA, cB)) return false; // touching this face
+            if (!tested || distance_squared(cA, cB) < distance_squared(r_A, r_B)) {
+                r_A = cA;
+                r_B = cB;
+                tested = true;
+            }
+        } else {
+            int right = __float_as_int(n1.w);
+            if (right >= 0 && sp < 63) stack[sp++] = right;
+            if (sp < 64) stack[sp++] = idx + 1;
+        }
+    }
+    return true;
+}
+
 // cast_motion (bradot_space_3d.cpp:264-381): how far the query shape can travel along `motion` before it touches anything --
 // per candidate a GJK distance test of the swept shape, then eight bisection steps on the travelled fraction.
 __global__ void __launch_bounds__(QS_THREADS) k_cast_motion(QsArgs a) {
@@ -237,17 +297,17 @@ __global__ void __launch_bounds__(QS_THREADS) k_cast_motion(QsArgs a) {
         // does it collide if going all the way?
         A.swept = true;
         A.motion = xform(xform_inv.b, motion);
-        if (solve_distance(A, B, point_A, point_B)) return;
+        if (solve_distance_any(A, B, qmin, qmax, point_A, point_B)) return;
         // objects it starts inside of are ignored
         A.swept = false;
-        if (!solve_distance(A, B, point_A, point_B)) return;
+        if (!solve_distance_any(A, B, qmin, qmax, point_A, point_B)) return;
         A.swept = true;
         float low = 0.0f, hi = 1.0f, fraction_coeff = 0.5f;
         for (int k = 0; k < 8; k++) {
             float fraction = low + (hi - low) * fraction_coeff;
             A.motion = xform(xform_inv.b, motion * fraction);
             V3 lA, lB;
-            bool collided = !solve_distance(A, B, lA, lB);
+            bool collided = !solve_distance_any(A, B, qmin, qmax, lA, lB);
             if (collided) {
                 hi = fraction;
                 // first time or alternating: bisect; colliding again: converge faster towards the low end
@@ -842,9 +902,9 @@ __global__ void __launch_bounds__(32) k_test_motion(MtArgs m) {
             V3 pA, pB;
             A.swept = true;
             A.motion = xform(inv.b, motion);
-            if (solve_distance(A, B, pA, pB)) return; // free all the way
+            if (solve_distance_any(A, B, bmin, bmax, pA, pB)) return; // free all the way
             A.swept = false;
-            if (!solve_distance(A, B, pA, pB)) { // overlapping where it stands
+            if (!solve_distance_any(A, B, bmin, bmax, pA, pB)) { // overlapping where it stands
                 stuck = true;
                 return;
             }
@@ -854,7 +914,7 @@ __global__ void __launch_bounds__(32) k_test_motion(MtArgs m) {
                 float fraction = low + (high - low) * coeff;
                 A.motion = xform(inv.b, motion * fraction);
                 V3 lA, lB;
-                bool collided = !solve_distance(A, B, lA, lB);
+                bool collided = !solve_distance_any(A, B, bmin, bmax, lA, lB);
                 if (collided) {
                     high = fraction;
                     coeff = ((k == 0) || (low > 0.0f)) ? 0.5f : 0.25f;

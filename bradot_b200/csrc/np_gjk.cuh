@@ -20,6 +20,8 @@ struct GjkBody {
     X3 x;
     V3 motion;
     bool swept;
+    bool is_face = false; // one face of a triangle mesh (BradotFaceShape3D::get_support, bradot_shape_3d.cpp:1189-1203): fv in the mesh's space
+    V3 fv[3];
 };
 
 // BradotShape3D::get_support for a unit direction in the shape's own space
@@ -59,6 +61,18 @@ __device__ inline V3 shape_support(const Sh &s, V3 n) {
 // MinkowskiDiff::Support0 / Support1 without margins: get_support(xform_inv(d).normalized()), swept shapes add their motion
 __device__ inline V3 gjk_support_of(const GjkBody &b, V3 d) {
     V3 n = normalized(xform_inv(b.x.b, d));
+    if (b.is_face) {
+        int best = 0;
+        float support_max = 0;
+        for (int i = 0; i < 3; i++) {
+            float dd = dot(n, b.fv[i]);
+            if (i == 0 || dd > support_max) {
+                support_max = dd;
+                best = i;
+            }
+        }
+        return xform(b.x, b.fv[best]);
+    }
     V3 sup = shape_support(b.s, n);
     if (b.swept && dot(n, b.motion) > 0) sup += b.motion;
     return xform(b.x, sup);

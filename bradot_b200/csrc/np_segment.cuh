@@ -176,6 +176,7 @@ __device__ inline bool q_shape_point_inside(const MeshPools &a, const QShape &s,
             q.y = fabsf(q.y) - height * 0.5f + radius;
             return length(q) < radius;
         }
+        case SH_CONCAVE: return false; // "face is flat" (bradot_shape_3d.cpp:1425-1427)
         default: {
             for (uint32_t i = 0; i < s.mesh.face_cnt; i++) {
                 float4 pl = a.mplanes[s.mesh.face_ofs + i];
@@ -186,8 +187,58 @@ __device__ inline bool q_shape_point_inside(const MeshPools &a, const QShape &s,
     }
 }
 
-__device__ inline bool q_shape_segment(const MeshPools &a, const QShape &s, V3 from, V3 to, RayHit &h) {
+// BradotConcavePolygonShape3D::intersect_segment / _cull_segment + BradotFaceShape3D::intersect_segment
+// (bradot_shape_3d.cpp:1350-1423, 1257-1271): the nearest face the segment crosses, front faces only unless the mesh collides
+// on both sides and the query asks for back faces.  Mesh layout: np_face.cuh.
+__device__ inline bool q_mesh_segment(const MeshPools &a, const MeshRec &mesh, V3 from, V3 to, bool hit_back_faces, RayHit &h) {
+    if (mesh.face_cnt == 0) return false;
+    const float4 *nodes = a.mplanes + mesh.face_ofs;
+    const bool both_sides = mesh.edge_cnt != 0 && hit_back_faces;
+    V3 dir = normalized(to - from);
+    float min_d = 1e20f;
+    int collisions = 0;
+    int stack[64];
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp) {
+        int idx = stack[--sp];
+        float4 n0 = nodes[2 * idx], n1 = nodes[2 * idx + 1];
+        V3 bpos = f4v(n0), bsize = f4v(n1);
+        if (!q_box_segment(bpos, bpos + bsize, from, to, nullptr, nullptr)) continue;
+        int face_index = __float_as_int(n0.w);
+        if (face_index >= 0) {
+            V3 v0 = f4v(a.mverts[mesh.vert_ofs + 3 * face_index]), v1 = f4v(a.mverts[mesh.vert_ofs + 3 * face_index + 1]),
+               v2 = f4v(a.mverts[mesh.vert_ofs + 3 * face_index + 2]);
+            V3 res;
+            if (q_triangle_segment(from, to, v0, v1, v2, res)) {
+                V3 normal = normalized(cross(v0 - v2, v0 - v1)); // Plane(v0, v1, v2).normal
+                bool c = true;
+                if (dot(normal, to - from) > 0) {
+                    if (both_sides) normal = -normal;
+                    else c = false;
+                }
+                if (c) {
+                    float d = dot(dir, res) - dot(dir, from);
+                    if ((d > 0) && (d < min_d)) {
+                        min_d = d;
+                        h.point = res;
+                        h.normal = normal;
+                        collisions++;
+                    }
+                }
+            }
+        } else {
+            int right = __float_as_int(n1.w);
+            if (right >= 0 && sp < 63) stack[sp++] = right;
+            if (sp < 64) stack[sp++] = idx + 1;
+        }
+    }
+    return collisions > 0;
+}
+
+__device__ inline bool q_shape_segment(const MeshPools &a, const QShape &s, V3 from, V3 to, RayHit &h, bool hit_back_faces = true) {
     switch (s.type) {
+        case SH_CONCAVE: return q_mesh_segment(a, s.mesh, from, to, hit_back_faces, h);
         case SH_PLANE: { // Plane::intersects_segment
             V3 n(s.p.x, s.p.y, s.p.z);
             V3 segment = from - to;

@@ -38,6 +38,7 @@ RID BradotPhysicsServerCUDA::sphere_shape_create() { MAKE_SHAPE(SHAPE_SPHERE) }
 RID BradotPhysicsServerCUDA::box_shape_create() { MAKE_SHAPE(SHAPE_BOX) }
 RID BradotPhysicsServerCUDA::capsule_shape_create() { MAKE_SHAPE(SHAPE_CAPSULE) }
 RID BradotPhysicsServerCUDA::convex_polygon_shape_create() { MAKE_SHAPE(SHAPE_CONVEX_POLYGON) }
+RID BradotPhysicsServerCUDA::concave_polygon_shape_create() { MAKE_SHAPE(SHAPE_CONCAVE_POLYGON) }
 
 void BradotPhysicsServerCUDA::shape_set_data(RID p_shape, const Variant &p_data) {
 	Shape *shape = shape_owner.get_or_null(p_shape);
@@ -125,6 +126,21 @@ int BradotPhysicsServerCUDA::_shape_handle(Shape *p_shape) {
 			p_shape->handle = bpc_shape_create_convex(ctx, verts.ptr(), mesh.vertices.size(), planes.ptr(), faces.ptr(), mesh.faces.size(),
 					indices.ptr(), indices.size(), edges.ptr(), mesh.edges.size());
 		} break;
+		case SHAPE_CONCAVE_POLYGON: {
+			// static triangle mesh: {"faces": three vertices per face, "backface_collision"}; the tree over the faces is built by
+			// the backend the way the reference builds its own (P3D/bradot_shape_3d.cpp:1614-1672)
+			Dictionary d = p_shape->data;
+			ERR_FAIL_COND_V(!d.has("faces"), -1);
+			Vector<Vector3> faces = d["faces"];
+			ERR_FAIL_COND_V(faces.size() == 0 || faces.size() % 3, -1);
+			LocalVector<float> f;
+			for (const Vector3 &v : faces) {
+				f.push_back(v.x);
+				f.push_back(v.y);
+				f.push_back(v.z);
+			}
+			p_shape->handle = bpc_shape_create_concave(ctx, f.ptr(), faces.size() / 3, bool(d.get("backface_collision", false)) ? 1 : 0, nullptr, 0, nullptr);
+		} break;
 		default:
 			ERR_FAIL_V_MSG(-1, "BradotPhysicsCUDA: unsupported shape type.");
 	}
@@ -179,7 +195,7 @@ struct BpcExcludeScope {
 	}
 };
 
-int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit) {
+int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces) {
 	ERR_FAIL_NULL_V(server, 0);
 	ERR_FAIL_COND_V(p_from_to.size() % 2, 0);
 	server->_flush_pending();
@@ -193,7 +209,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 	}
 	LocalVector<bpc_ray_result> out;
 	out.resize(n);
-	ERR_FAIL_COND_V_MSG(bpc_space_intersect_rays(server->ctx, space_handle, n, in.ptr(), p_collision_mask, p_hit_from_inside ? BPC_RAY_HIT_FROM_INSIDE : 0, out.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_rays(server->ctx, space_handle, n, in.ptr(), p_collision_mask, (p_hit_from_inside ? BPC_RAY_HIT_FROM_INSIDE : 0) | (p_hit_back_faces ? BPC_RAY_HIT_BACK_FACES : 0), out.ptr()) < 0, 0, bpc_last_error(server->ctx));
 	r_results.resize(n);
 	r_hit.resize(n);
 	int hits = 0;
@@ -389,7 +405,7 @@ bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_par
 	ft.push_back(p_parameters.to);
 	LocalVector<RayResult> res;
 	LocalVector<bool> hit;
-	if (intersect_rays_batch(ft, p_parameters.collision_mask, p_parameters.hit_from_inside, res, hit) != 1) {
+	if (intersect_rays_batch(ft, p_parameters.collision_mask, p_parameters.hit_from_inside, res, hit, p_parameters.hit_back_faces) != 1) {
 		return false;
 	}
 	r_result = res[0];

@@ -35,7 +35,7 @@ public:
 	int space_handle = -1;
 
 	virtual bool intersect_ray(const RayParameters &p_parameters, RayResult &r_result) override;
-	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit);
+	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces = true);
 	virtual int intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
 	virtual int intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
 	virtual bool cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info = nullptr) override;
@@ -256,6 +256,7 @@ public:
 	virtual RID box_shape_create() override;
 	virtual RID capsule_shape_create() override;
 	virtual RID convex_polygon_shape_create() override;
+	virtual RID concave_polygon_shape_create() override;
 	virtual void shape_set_data(RID p_shape, const Variant &p_data) override;
 	virtual ShapeType shape_get_type(RID p_shape) const override;
 	virtual Variant shape_get_data(RID p_shape) const override;

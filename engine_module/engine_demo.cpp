@@ -199,6 +199,18 @@ int main(int argc, char **argv) {
 				}
 				ps->shape_set_data(sh, pts);
 			} break;
+			case PhysicsServer3D::SHAPE_CONCAVE_POLYGON: {
+				sh = ps->concave_polygon_shape_create();
+				Vector<Vector3> pts;
+				for (uint32_t k = 0; k < s.vert_cnt; k++) {
+					const float *v = &verts[(s.vert_ofs + k) * 3];
+					pts.push_back(Vector3(v[0], v[1], v[2]));
+				}
+				Dictionary d;
+				d["faces"] = pts;
+				d["backface_collision"] = s.p[0] != 0.f;
+				ps->shape_set_data(sh, d);
+			} break;
 			default:
 				fprintf(stderr, "unsupported shape\n");
 				return 2;

@@ -131,8 +131,9 @@ int bpc_shape_create_convex(bpc_context *ctx, const float *verts, int n_verts, c
  * own (median split along the longest axis, P3D/bradot_shape_3d.cpp:1541-1586) unless one is handed over: bvh_nodes = n_nodes x 9
  * floats (box position, box size, left, right, face index or -1) in pre-order, normals = n_faces x 3 -- what the tests do with
  * the reference's own tree, so that faces are met in its order.  Against a mesh: the step (all four body shapes), intersect_shape,
- * collide_shape, rest_info, body_test_motion's recovery and rest steps.  Not built: rays and points against a mesh, the GJK
- * distance to a mesh (cast_motion and the cast of body_test_motion pass through it), HeightMapShape3D. */
+ * collide_shape, rest_info, body_test_motion's recovery and rest steps, intersect_ray (nearest face; a point is never inside a
+ * mesh), cast_motion and the cast of body_test_motion (GJK distance face by face).  Not built: HeightMapShape3D; continuous
+ * collision detection against a mesh. */
 int bpc_shape_create_concave(bpc_context *ctx, const float *faces, int n_faces, int backface_collision, const float *bvh_nodes, int n_nodes,
                              const float *normals);
 
@@ -280,7 +281,7 @@ int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order);
  * one space -- closest hit along each segment, bodies whose collision layer meets collision_mask, a shape the ray starts
  * inside is ignored unless BPC_RAY_HIT_FROM_INSIDE.  from_to: n x (from xyz, to xyz), host; out: n records, host.
  * `body` is the body slot (what the engine module maps back to a RID / ObjectID), -1 for a miss.
- * Exclude lists: bpc_space_set_query_exclude below.  Not built: areas, pick_ray, face_index (no concave shapes yet). */
+ * Exclude lists: bpc_space_set_query_exclude below.  Not built: areas, pick_ray, face_index. */
 typedef struct bpc_ray_result {
     int32_t hit;
     int32_t body;
@@ -288,7 +289,7 @@ typedef struct bpc_ray_result {
     float normal[3];
 } bpc_ray_result;
 #define BPC_RAY_HIT_FROM_INSIDE 1
-#define BPC_RAY_HIT_BACK_FACES 2 /* accepted; only concave shapes look at it */
+#define BPC_RAY_HIT_BACK_FACES 2 /* RayParameters::hit_back_faces (default on in the engine): a two-sided triangle mesh is also hit from behind */
 int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *from_to, unsigned collision_mask, int flags,
                              bpc_ray_result *out);
 

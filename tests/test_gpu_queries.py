@@ -322,3 +322,74 @@ def test_body_test_motion_against_the_reference():
             hits += len(sel)
         assert total > 60 and hits > 30, (total, hits)
         ps.finish()
+
+
+def test_queries_against_a_triangle_mesh():
+    """intersect_ray (BradotConcavePolygonShape3D::intersect_segment, bradot_shape_3d.cpp:1350-1423), intersect_shape, collide_shape
+    and rest_info (solve_concave + the *_face routines) where the space holds triangle meshes: the terrain scene, the GPU using
+    the reference's own tree over the faces.  Same bars as for the other shapes."""
+    parity_needed()
+    sc = scenes.terrain_pile()
+    rays = _rays(3000, 41, 3.8, 4.0)
+    rays[:1500, 1] = np.random.default_rng(1).uniform(1.5, 4.0, 1500)       # half of them start above the terrain ...
+    rays[:1500, 3:6] = rays[:1500, 0:3] + np.random.default_rng(2).normal(size=(1500, 3)) * 0.5 + np.array([0, -4.0, 0])   # ... and point down at it
+    rays = rays.astype(np.float32)
+    _, dump = parity.run_oracle(sc, 60, dump_from=0, dump_every=1, rays=rays, motions=True)
+    ps = parity.new_server(sc, dump)
+    shape_of = _shape_queries(ps, rays)
+    mesh_hits = mesh_stops = 0
+    for k in (1, 30, 59):
+        parity.load_state(ps, dump, k)
+        hit, body, pos, nrm = ps.intersect_rays(rays)
+        ref = dump[("rays", k)]
+        rhit = ref[:, 0] > 0
+        same = hit == rhit
+        assert same.mean() > 0.999, (k, int((~same).sum()))
+        both = hit & rhit
+        agree = body[both] == ref[both, 1].astype(np.int64)
+        assert agree.mean() > 0.999, (k, int((~agree).sum()))
+        sel = np.nonzero(both)[0][agree]
+        assert np.max(np.abs(pos[sel] - ref[sel, 2:5])) < POS_TOL and np.max(np.abs(nrm[sel] - ref[sel, 5:8])) < NRM_TOL, k
+        mesh_hits += int(np.isin(body[sel], (1, 2)).sum())
+        xf = dump[("shape_query_xf", k)]
+        counts, bodies = ps.intersect_shapes(shape_of, xf, max_results=8)
+        refq = dump[("shape_queries", k)]
+        differ = sum(set(bodies[i, :counts[i]].tolist()) != set(refq[i, 1:1 + refq[i, 0]].tolist()) for i in range(len(rays)) if refq[i, 0] < 8 and counts[i] < 8)
+        assert differ <= len(rays) // 500, (k, differ)
+        d = rays[:, 3:6] - rays[:, 0:3]
+        motions = (d / np.linalg.norm(d, axis=1, keepdims=True) * np.float32(0.01)).astype(np.float32)
+        odd = np.arange(len(rays)) % 2 == 1
+        out = np.zeros(len(rays), server.REST_INFO_DT)
+        out[odd] = ps.rest_infos(shape_of[odd], xf[odd], motions[odd], margin=0.04)
+        out[~odd] = ps.rest_infos(shape_of[~odd], xf[~odd], motions[~odd], margin=0.0)
+        refr = dump[("shape_rest", k)]
+        sameh = (out["hit"] > 0) == (refr[:, 0] > 0)
+        assert sameh.mean() > 0.995, (k, int((~sameh).sum()))
+        bothr = (out["hit"] > 0) & (refr[:, 0] > 0)
+        agr = out["body"][bothr] == refr[bothr, 1].astype(np.int32)
+        assert agr.mean() > 0.98, (k, int((~agr).sum()))
+        s2 = np.nonzero(bothr)[0][agr]
+        close = (np.abs(out["point"][s2] - refr[s2, 2:5]).max(axis=1) < POS_TOL) & (np.abs(out["normal"][s2] - refr[s2, 5:8]).max(axis=1) < NRM_TOL)
+        assert close.mean() > 0.98, (k, int((~close).sum()))
+        assert int(np.isin(out["body"][s2], (1, 2)).sum()) > 20
+        # cast_motion: the GJK distance to the faces of the mesh (solve_distance's concave branch)
+        fr, info = ps.cast_motions(shape_of, xf, ((rays[:, 3:6] - rays[:, 0:3]) * np.float32(0.5)).astype(np.float32))
+        refc = dump[("shape_cast", k)]
+        exact = np.all(fr == refc[:, 0:2], axis=1)
+        assert exact.mean() > 0.99, (k, int((~exact).sum()))
+        stop = exact & (info["hit"] > 0) & (refc[:, 2] > 0)
+        same_body = info["body"][stop] == refc[stop, 3].astype(np.int32)
+        assert same_body.mean() > 0.98
+        mesh_stops += int(np.isin(info["body"][stop][same_body], (1, 2)).sum())
+        # body_test_motion of the bodies lying on the mesh
+        q, refm = dump[("motion_queries", k)], dump[("motion_results", k)]
+        prm = np.zeros(len(q), server.MOTION_PARAMS_DT)
+        prm["body"], prm["from"], prm["motion"] = q[:, 0].astype(np.int32), q[:, 1:13], q[:, 13:16]
+        prm["margin"], prm["max_collisions"], prm["flags"] = q[:, 16], q[:, 17].astype(np.int32), q[:, 18].astype(np.uint32)
+        mo = ps.bodies_test_motion(prm)
+        assert np.array_equal(mo["collided"] > 0, refm[:, 0] > 0)
+        hitm = refm[:, 0] > 0
+        assert (not hitm.any() or np.mean(mo["collision_safe_fraction"][hitm] == refm[hitm, 9]) >= 0.8) and np.max(np.abs(mo["travel"] - refm[:, 2:5])) < 2e-2
+        motion_hits = motion_hits + int(hitm.sum()) if k > 1 else 0
+    assert mesh_hits > 1000 and mesh_stops > 300 and motion_hits > 5
+    ps.finish()
