@@ -442,6 +442,41 @@ extern "C" int bpc_shape_create_concave(bpc_context *ctx, const float *faces, in
     return (int)ctx->h_shapes.size() - 1;
 }
 
+
+// HeightMapShape3D (P3D/bradot_shape_3d.cpp:2159-2178): width x depth heights, one unit apart, centred on the shape's origin
+extern "C" int bpc_shape_create_heightmap(bpc_context *ctx, const float *heights, int width, int depth, float min_height, float max_height) {
+    if (!ctx) return -1;
+    if (width < 2 || depth < 2 || !heights) return fail(ctx, "bpc_shape_create_heightmap: needs at least 2 x 2 heights");
+    if (min_height > max_height) return fail(ctx, "bpc_shape_create_heightmap: min_height above max_height");
+    MeshRec m;
+    memset(&m, 0, sizeof(m));
+    m.vert_ofs = (uint32_t)ctx->h_mverts.size();
+    m.vert_cnt = (uint32_t)width; // MeshView.nv / .nf of a height map are its width / depth
+    m.face_ofs = (uint32_t)ctx->h_mplanes.size();
+    m.face_cnt = (uint32_t)depth;
+    m.edge_ofs = (uint32_t)ctx->h_medges.size();
+    m.index_ofs = (uint32_t)ctx->h_mindex.size();
+    m.scan_all = 3; // marks a height map
+    size_t n = (size_t)width * depth;
+    for (size_t i = 0; i < n; i += 4) {
+        float h[4] = { 0.f, 0.f, 0.f, 0.f };
+        for (size_t k = 0; k < 4 && i + k < n; k++) h[k] = heights[i + k];
+        ctx->h_mverts.push_back(make_float4(h[0], h[1], h[2], h[3]));
+    }
+    ShapeRec r;
+    memset(&r, 0, sizeof(r));
+    r.meta = make_uint4(SH_HEIGHTMAP, (uint32_t)ctx->h_meshes.size(), 0, 0);
+    // aabb: position (0, min, 0) - local_origin, size (width - 1, max - min, depth - 1); local_origin = position + 0.5 size with y = 0
+    float sx = (float)(width - 1), sy = max_height - min_height, sz = (float)(depth - 1);
+    float ox = 0.0f + (float)(0.5 * (double)sx), oz = 0.0f + (float)(0.5 * (double)sz);
+    r.aabb_pos = make_float4(0.0f - ox, min_height - 0.0f, 0.0f - oz, 0.f);
+    r.aabb_size = make_float4(sx, sy, sz, 0.f);
+    ctx->h_meshes.push_back(m);
+    ctx->h_shapes.push_back(r);
+    ctx->shapes_dirty = true;
+    return (int)ctx->h_shapes.size() - 1;
+}
+
 template <typename T>
 static int upload(bpc_context *ctx, DevBuf<T> &d, const std::vector<T> &h) {
     if (h.empty()) return 0;

@@ -212,8 +212,8 @@ static int validate_descs(bpc_context *ctx, const bpc_body_desc *descs, int n, c
     for (int i = 0; i < n; i++) {
         if (descs[i].space >= ctx->spaces.size() || !ctx->spaces[descs[i].space].alive) return fail(ctx, (std::string(who) + ": invalid space").c_str());
         if (descs[i].shape >= ctx->h_shapes.size()) return fail(ctx, (std::string(who) + ": invalid shape").c_str());
-        if (ctx->h_shapes[descs[i].shape].meta.x == SH_CONCAVE && descs[i].mode != MODE_STATIC)
-            return fail(ctx, (std::string(who) + ": a triangle mesh can only be the shape of a static body").c_str());
+        if (ctx->h_shapes[descs[i].shape].meta.x >= SH_CONCAVE && descs[i].mode != MODE_STATIC)
+            return fail(ctx, (std::string(who) + ": a triangle mesh or a height map can only be the shape of a static body").c_str());
         if (descs[i].mode > MODE_RIGID_LINEAR) return fail(ctx, (std::string(who) + ": invalid body mode").c_str());
     }
     return 0;
@@ -285,7 +285,7 @@ static int write_body_slots(bpc_context *ctx, const uint32_t *slots, const bpc_b
         meta[i] = make_uint4(d.mode | (flags << 8) | (sh.meta.x << 24), d.layer, d.mask, d.space);
         sp[i] = sh.p;
         ctx->shape_type_mask |= 1u << sh.meta.x;
-        if (sh.meta.x == SH_CONVEX || sh.meta.x == SH_CONCAVE) memcpy(&sp[i].x, &sh.meta.y, 4);
+        if (sh.meta.x >= SH_CONVEX) memcpy(&sp[i].x, &sh.meta.y, 4);
         sid[i] = d.shape;
         ctx->h_mode[slot] = (uint8_t)d.mode;
         ctx->h_space_of[slot] = d.space;

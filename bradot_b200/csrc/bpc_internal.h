@@ -11,7 +11,7 @@
 
 // ---- shape / body enums: numeric values of the reference enums -------------------------------
 // servers/physics_server_3d.h:247-259 (ShapeType) and :387-392 (BodyMode)
-enum { SH_PLANE = 0, SH_RAY = 1, SH_SPHERE = 2, SH_BOX = 3, SH_CAPSULE = 4, SH_CYLINDER = 5, SH_CONVEX = 6, SH_CONCAVE = 7 };
+enum { SH_PLANE = 0, SH_RAY = 1, SH_SPHERE = 2, SH_BOX = 3, SH_CAPSULE = 4, SH_CYLINDER = 5, SH_CONVEX = 6, SH_CONCAVE = 7, SH_HEIGHTMAP = 8 };
 enum { MODE_STATIC = 0, MODE_KINEMATIC = 1, MODE_RIGID = 2, MODE_RIGID_LINEAR = 3 };
 
 // body flag bits (meta.x = mode | flags << 8)

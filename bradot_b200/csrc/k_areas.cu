@@ -44,7 +44,7 @@ __device__ __forceinline__ Sh ar_shape(const ArArgs &a, uint32_t type, float4 p)
     s.type = type;
     s.p = p;
     s.m.nv = s.m.nf = s.m.ne = 0;
-    if (type == SH_CONVEX || type == SH_CONCAVE) {
+    if (type >= SH_CONVEX) {
         MeshRec m = a.meshes[__float_as_uint(p.x)];
         s.m.verts = a.mverts + m.vert_ofs;
         s.m.planes = a.mplanes + m.face_ofs;
@@ -198,7 +198,7 @@ static int area_from_desc(bpc_context *ctx, const bpc_area_desc &d, AreaRec &r) 
     r.s2 = make_float4(s[6], s[7], s[8], 0.f);
     r.so = make_float4(s[9], s[10], s[11], 0.f);
     r.shape_p = sh.p;
-    if (sh.meta.x == SH_CONVEX || sh.meta.x == SH_CONCAVE) memcpy(&r.shape_p.x, &sh.meta.y, 4);
+    if (sh.meta.x >= SH_CONVEX) memcpy(&r.shape_p.x, &sh.meta.y, 4);
     r.shape_type = sh.meta.x;
     r.space = (uint32_t)d.space;
     r.layer = d.layer;

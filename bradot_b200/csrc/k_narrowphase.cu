@@ -47,7 +47,7 @@ __device__ __forceinline__ Sh load_shape(const NpArgs &a, uint32_t sid) {
     s.type = r.meta.x;
     s.p = r.p;
     s.m.nv = s.m.nf = s.m.ne = 0;
-    if (s.type == SH_CONVEX || s.type == SH_CONCAVE) {
+    if (s.type >= SH_CONVEX) { // hulls, triangle meshes and height maps live in the mesh pools
         MeshRec m = a.meshes[r.meta.y];
         s.m.verts = a.mverts + m.vert_ofs;
         s.m.planes = a.mplanes + m.face_ofs;
@@ -69,7 +69,7 @@ __device__ __forceinline__ Sh load_shape_fast(const NpArgs &a, uint32_t body, ui
     s.type = meta_x >> 24;
     s.p = a.shape_p[body];
     s.m.nv = s.m.nf = s.m.ne = 0;
-    if (s.type == SH_CONVEX || s.type == SH_CONCAVE) {
+    if (s.type >= SH_CONVEX) { // hulls, triangle meshes and height maps live in the mesh pools
         MeshRec m = a.meshes[__float_as_uint(s.p.x)];
         s.m.verts = a.mverts + m.vert_ofs;
         s.m.planes = a.mplanes + m.face_ofs;
@@ -402,7 +402,7 @@ int bpc_launch_narrowphase(bpc_context *ctx) {
         a.perm = ctx->vals.p;
     }
     // (scenes without a triangle mesh run the instances compiled without that branch: same code as before meshes existed)
-    const bool mesh = (ctx->shape_type_mask >> SH_CONCAVE) & 1u;
+    const bool mesh = ((ctx->shape_type_mask >> SH_CONCAVE) & 3u) != 0u;
     if (mesh) k_pair_test<true><<<(n + 127) / 128, 128, 0, ctx->stream>>>(a);
     else k_pair_test<false><<<(n + 127) / 128, 128, 0, ctx->stream>>>(a);
     // the survivor count stays on the device: launch for the worst case, surplus threads exit at once

@@ -70,7 +70,7 @@ __device__ inline bool q_ray_candidate(const QArgs &a, uint32_t j, V3 begin, V3 
     QShape s;
     s.type = m.x >> 24;
     s.p = a.shape_p[j];
-    if (s.type == SH_CONVEX || s.type == SH_CONCAVE) s.mesh = a.pools.meshes[__float_as_uint(s.p.x)];
+    if (s.type >= SH_CONVEX) s.mesh = a.pools.meshes[__float_as_uint(s.p.x)];
     if (q_shape_point_inside(a.pools, s, local_from)) {
         if (a.flags & 1u) { // hit_from_inside
             best.min_d = 0.f;
@@ -181,7 +181,7 @@ __device__ inline void q_point_candidate(const PArgs &a, uint32_t j, V3 point, u
     QShape s;
     s.type = m.x >> 24;
     s.p = a.q.shape_p[j];
-    if (s.type == SH_CONVEX || s.type == SH_CONCAVE) s.mesh = a.q.pools.meshes[__float_as_uint(s.p.x)];
+    if (s.type >= SH_CONVEX) s.mesh = a.q.pools.meshes[__float_as_uint(s.p.x)];
     if (!q_shape_point_inside(a.q.pools, s, xform(inv_xform, point))) return;
     a.bodies[(size_t)r * a.max_results + cc] = (int32_t)j;
     cc++;

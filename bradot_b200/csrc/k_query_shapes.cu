@@ -51,7 +51,7 @@ __device__ __forceinline__ Sh qs_shape(const QsArgs &a, uint32_t type, float4 p)
     s.type = type;
     s.p = p;
     s.m.nv = s.m.nf = s.m.ne = 0;
-    if (type == SH_CONVEX || type == SH_CONCAVE) {
+    if (type >= SH_CONVEX) {
         MeshRec m = a.meshes[__float_as_uint(p.x)];
         s.m.verts = a.mverts + m.vert_ofs;
         s.m.planes = a.mplanes + m.face_ofs;
@@ -128,7 +128,7 @@ __device__ inline void qs_for_candidates(const QsArgs &a, V3 qmin, V3 qmax, F f)
 __device__ inline void qs_request(const QsArgs &a, uint32_t r, float grow, Sh &qs, X3 &qx, V3 &qmin, V3 &qmax) {
     const ShapeRec sr = a.shapes[a.shape_ids[r]];
     float4 p = sr.p;
-    if (sr.meta.x == SH_CONVEX || sr.meta.x == SH_CONCAVE) p.x = __uint_as_float(sr.meta.y);
+    if (sr.meta.x >= SH_CONVEX) p.x = __uint_as_float(sr.meta.y);
     qs = qs_shape(a, sr.meta.x, p);
     const float *f = a.xforms + (size_t)r * 12;
     qx = X3(M3(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8])), V3(f[9], f[10], f[11]));
@@ -209,10 +209,8 @@ __global__ void __launch_bounds__(QS_THREADS) k_rest_info(QsArgs a) {
 // GJK distance (concave_distance_callback, :437-457); the first face touched ends the walk, else the closest pair of points
 // over the faces tried is the answer.
 __device__ inline bool solve_distance_any(const GjkBody &A, const GjkBody &B, V3 hint_min, V3 hint_max, V3 &r_A, V3 &r_B) {
-    if (B.s.type != SH_CONCAVE) return solve_distance(A, B, r_A, r_B);
-    const MeshView &m = B.s.m;
+    if (B.s.type < SH_CONCAVE) return solve_distance(A, B, r_A, r_B);
     r_A = r_B = V3();
-    if (m.nf == 0) return true;
     V3 hpos = hint_min - B.x.o, hsize = hint_max - hint_min;
     V3 half(hsize.x * 0.5f, hsize.y * 0.5f, hsize.z * 0.5f);
     V3 center(hpos.x + half.x, hpos.y + half.y, hpos.z + half.z);
@@ -230,38 +228,28 @@ __device__ inline bool solve_distance_any(const GjkBody &A, const GjkBody &B, V3
         lpos[i] = smin;
         lsize[i] = smax - smin;
     }
-    const float4 *nodes = m.planes;
     GjkBody F;
     F.s = B.s;
     F.x = B.x;
     F.motion = V3();
     F.swept = false;
     F.is_face = true;
-    bool tested = false;
-    int stack[64];
-    int sp = 0;
-    stack[sp++] = 0;
-    while (sp) {
-        int idx = stack[--sp];
-        float4 n0 = __ldg(&nodes[2 * idx]), n1 = __ldg(&nodes[2 * idx + 1]);
-        if (!aabb_intersects(lpos, lsize, f4v(n0), f4v(n1))) continue;
-        int face_index = __float_as_int(n0.w);
-        if (face_index >= 0) {
-            for (int v = 0; v < 3; v++) F.fv[v] = mv_vert(m, 3 * face_index + v);
-            V3 cA, cB;
-            if (!gjk_distance(A, F, cA, cB)) return false; // touching this face
-            if (!tested || distance_squared(cA, cB) < distance_squared(r_A, r_B)) {
-                r_A = cA;
-                r_B = cB;
-                tested = true;
-            }
-        } else {
-            int right = __float_as_int(n1.w);
-            if (right >= 0 && sp < 63) stack[sp++] = right;
-            if (sp < 64) stack[sp++] = idx + 1;
+    bool tested = false, collided = false;
+    mesh_cull(B.s, lpos, lsize, [&](const FaceSh &f) -> bool {
+        for (int v = 0; v < 3; v++) F.fv[v] = f.v[v];
+        V3 cA, cB;
+        if (!gjk_distance(A, F, cA, cB)) { // touching this face
+            collided = true;
+            return true;
         }
-    }
-    return true;
+        if (!tested || distance_squared(cA, cB) < distance_squared(r_A, r_B)) {
+            r_A = cA;
+            r_B = cB;
+            tested = true;
+        }
+        return false;
+    });
+    return !collided;
 }
 
 // cast_motion (bradot_space_3d.cpp:264-381): how far the query shape can travel along `motion` before it touches anything --
@@ -353,7 +341,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
     if (r >= a.n) return;
     const ShapeRec sr = a.shapes[a.shape_ids[r]];
     float4 p = sr.p;
-    if (sr.meta.x == SH_CONVEX || sr.meta.x == SH_CONCAVE) p.x = __uint_as_float(sr.meta.y);
+    if (sr.meta.x >= SH_CONVEX) p.x = __uint_as_float(sr.meta.y);
     Sh qs = qs_shape(a, sr.meta.x, p);
     const float *f = a.xforms + (size_t)r * 12;
     X3 qx(M3(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8])), V3(f[9], f[10], f[11]));
@@ -429,7 +417,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
     if (r >= a.n) return;
     const ShapeRec sr = a.shapes[a.shape_ids[r]];
     float4 p = sr.p;
-    if (sr.meta.x == SH_CONVEX || sr.meta.x == SH_CONCAVE) p.x = __uint_as_float(sr.meta.y);
+    if (sr.meta.x >= SH_CONVEX) p.x = __uint_as_float(sr.meta.y);
     Sh qs = qs_shape(a, sr.meta.x, p);
     const float *f = a.xforms + (size_t)r * 12;
     X3 qx(M3(V3(f[0], f[1], f[2]), V3(f[3], f[4], f[5]), V3(f[6], f[7], f[8])), V3(f[9], f[10], f[11]));

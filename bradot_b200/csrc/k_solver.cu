@@ -168,6 +168,7 @@ __device__ __noinline__ void load_ccd_shape(const SvArgs &a, uint32_t body, uint
     out.sh.m.nv = out.sh.m.nf = out.sh.m.ne = 0;
     out.qs.type = out.sh.type;
     out.qs.p = out.sh.p;
+    if (out.sh.type > SH_CONVEX) out.qs.mesh = a.pools.meshes[__float_as_uint(out.sh.p.x)]; // a mesh: only ever the side the segment is cast at
     if (out.sh.type == SH_CONVEX) {
         MeshRec m = a.pools.meshes[__float_as_uint(out.sh.p.x)];
         out.qs.mesh = m;

@@ -336,11 +336,79 @@ __device__ inline bool collide_face(const Sh &a, const X3 &xa, const FaceSh &f, 
     return c.collided;
 }
 
+// The faces of a triangle mesh or a height map whose boxes meet the box (lpos, lsize) given in the shape's own space, in the
+// reference's order; f(face) returns true to end the walk.
+//   triangle mesh: BradotConcavePolygonShape3D::_cull (bradot_shape_3d.cpp:1433-1465), depth first, left before right
+//   height map:    BradotHeightMapShape3D::cull (:2028-2078), the cells under the box row by row, two faces each, both sides
+//                  solid.  MeshView of a height map: verts = the heights, four to a float4, row by row; nv = width, nf = depth.
+template <typename F>
+__device__ inline void mesh_cull(const Sh &mesh, V3 lpos, V3 lsize, F f) {
+    const MeshView &m = mesh.m;
+    FaceSh face;
+    if (mesh.type == SH_HEIGHTMAP) {
+        const int width = (int)m.nv, depth = (int)m.nf;
+        const V3 local_origin((float)(0.5 * (double)(width - 1)), 0.f, (float)(0.5 * (double)(depth - 1)));
+        auto height_at = [&](int x, int z) -> float {
+            int i = z * width + x;
+            float4 h4 = __ldg(&m.verts[i >> 2]);
+            return (i & 3) == 0 ? h4.x : (i & 3) == 1 ? h4.y : (i & 3) == 2 ? h4.z : h4.w;
+        };
+        auto point_at = [&](int x, int z) -> V3 {
+            return V3((float)((double)x - 0.5 * ((double)width - 1.0)), height_at(x, z), (float)((double)z - 0.5 * ((double)depth - 1.0)));
+        };
+        auto cell_of = [&](float v, float hi) -> int { // _get_cell: clamp to the shape's box, round half away from zero
+            float c = fminf(fmaxf(v, 0.f), hi);
+            return (int)((c < 0.0f) ? ((double)c - 0.5) : ((double)c + 0.5));
+        };
+        V3 lo = lpos + local_origin, hi = lpos + local_origin + lsize;
+        int min_x = cell_of(lo.x, (float)(width - 1)) - 1, max_x = cell_of(hi.x, (float)(width - 1)) + 1;
+        int min_z = cell_of(lo.z, (float)(depth - 1)) - 1, max_z = cell_of(hi.z, (float)(depth - 1)) + 1;
+        int start_x = max(0, min_x), end_x = min(width - 1, max_x), start_z = max(0, min_z), end_z = min(depth - 1, max_z);
+        face.backface_collision = true;
+        for (int z = start_z; z < end_z; z++) {
+            for (int x = start_x; x < end_x; x++) {
+                face.v[0] = point_at(x, z);
+                face.v[1] = point_at(x + 1, z);
+                face.v[2] = point_at(x, z + 1);
+                face.normal = normalized(cross(face.v[0] - face.v[2], face.v[0] - face.v[1]));
+                if (f(face)) return;
+                face.v[0] = face.v[1];
+                face.v[1] = point_at(x + 1, z + 1);
+                face.normal = normalized(cross(face.v[0] - face.v[2], face.v[0] - face.v[1]));
+                if (f(face)) return;
+            }
+        }
+        return;
+    }
+    if (m.nf == 0) return;
+    const float4 *nodes = m.planes;
+    const float4 *normals = m.planes + 2 * (size_t)m.nf;
+    face.backface_collision = m.ne != 0;
+    int stack[64]; // a median-split tree over n faces is ceil(log2 n) + 1 deep
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp) {
+        int idx = stack[--sp];
+        float4 n0 = __ldg(&nodes[2 * idx]), n1 = __ldg(&nodes[2 * idx + 1]);
+        if (!aabb_intersects(lpos, lsize, f4v(n0), f4v(n1))) continue;
+        int face_index = __float_as_int(n0.w);
+        if (face_index >= 0) {
+            face.normal = f4v(__ldg(&normals[face_index]));
+            face.v[0] = mv_vert(m, 3 * face_index + 0);
+            face.v[1] = mv_vert(m, 3 * face_index + 1);
+            face.v[2] = mv_vert(m, 3 * face_index + 2);
+            if (f(face)) return;
+        } else {
+            int right = __float_as_int(n1.w);
+            if (right >= 0 && sp < 63) stack[sp++] = right; // popped after the whole left subtree
+            if (sp < 64) stack[sp++] = idx + 1;
+        }
+    }
+}
+
 // BradotCollisionSolver3D::solve_concave: `mesh` is shape B.  In TEST mode the walk stops at the first colliding face.
 template <bool TEST, bool MG>
 __device__ inline bool solve_concave(const Sh &a, const X3 &xa, const Sh &mesh, const X3 &xb, Collector &c, bool swap_result, float margin_A) {
-    const MeshView &m = mesh.m;
-    if (m.nf == 0) return false;
     X3 rel = xa;
     rel.o -= xb.o;
     V3 lpos, lsize;
@@ -357,34 +425,14 @@ __device__ inline bool solve_concave(const Sh &a, const X3 &xa, const Sh &mesh, 
         lpos[i] = smin;
         lsize[i] = smax - smin;
     }
-    const float4 *nodes = m.planes;
-    const float4 *normals = m.planes + 2 * (size_t)m.nf;
-    FaceSh f;
-    f.backface_collision = m.ne != 0;
     bool collided = false;
-    int stack[64]; // a median-split tree over n faces is ceil(log2 n) + 1 deep
-    int sp = 0;
-    stack[sp++] = 0;
-    while (sp) {
-        int idx = stack[--sp];
-        float4 n0 = __ldg(&nodes[2 * idx]), n1 = __ldg(&nodes[2 * idx + 1]);
-        if (!aabb_intersects(lpos, lsize, f4v(n0), f4v(n1))) continue;
-        int face_index = __float_as_int(n0.w);
-        if (face_index >= 0) {
-            f.normal = f4v(__ldg(&normals[face_index]));
-            f.v[0] = mv_vert(m, 3 * face_index + 0);
-            f.v[1] = mv_vert(m, 3 * face_index + 1);
-            f.v[2] = mv_vert(m, 3 * face_index + 2);
-            if (collide_face<TEST, MG>(a, xa, f, xb, c, swap_result)) {
-                collided = true;
-                if (TEST) return true;
-            }
-        } else {
-            int right = __float_as_int(n1.w);
-            if (right >= 0 && sp < 63) stack[sp++] = right; // popped after the whole left subtree
-            if (sp < 64) stack[sp++] = idx + 1;
+    mesh_cull(mesh, lpos, lsize, [&](const FaceSh &f) -> bool {
+        if (collide_face<TEST, MG>(a, xa, f, xb, c, swap_result)) {
+            collided = true;
+            return TEST;
         }
-    }
+        return false;
+    });
     c.collided = collided;
     return collided;
 }

@@ -530,8 +530,8 @@ __device__ inline bool solve_static(const Sh &sa, const X3 &xa, const Sh &sb, co
         if (ta > tb) return col_plane<TEST, MG>(sb, xb, sa, xa, c, true, margin_A);
         return col_plane<TEST, MG>(sa, xa, sb, xb, c, false, margin_B);
     }
-    if (MESH && max(ta, tb) == SH_CONCAVE) { // a static triangle mesh: the other shape against every face its box meets
-        if (ta == SH_CONCAVE && tb == SH_CONCAVE) return false;
+    if (MESH && max(ta, tb) >= SH_CONCAVE) { // a static triangle mesh or height map: the other shape against every face its box meets
+        if (ta >= SH_CONCAVE && tb >= SH_CONCAVE) return false;
         if (MG) {
             c.margin_A = margin_A; // (solve_concave hands both margins on unswapped, ...collision_solver_3d.cpp:425-429)
             c.margin_B = margin_B;

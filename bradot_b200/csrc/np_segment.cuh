@@ -176,7 +176,8 @@ __device__ inline bool q_shape_point_inside(const MeshPools &a, const QShape &s,
             q.y = fabsf(q.y) - height * 0.5f + radius;
             return length(q) < radius;
         }
-        case SH_CONCAVE: return false; // "face is flat" (bradot_shape_3d.cpp:1425-1427)
+        case SH_CONCAVE:
+        case SH_HEIGHTMAP: return false; // "face is flat" (bradot_shape_3d.cpp:1425-1427, 2007-2009)
         default: {
             for (uint32_t i = 0; i < s.mesh.face_cnt; i++) {
                 float4 pl = a.mplanes[s.mesh.face_ofs + i];
@@ -239,6 +240,7 @@ __device__ inline bool q_mesh_segment(const MeshPools &a, const MeshRec &mesh, V
 __device__ inline bool q_shape_segment(const MeshPools &a, const QShape &s, V3 from, V3 to, RayHit &h, bool hit_back_faces = true) {
     switch (s.type) {
         case SH_CONCAVE: return q_mesh_segment(a, s.mesh, from, to, hit_back_faces, h);
+        case SH_HEIGHTMAP: return false; // the grid walk of BradotHeightMapShape3D::intersect_segment is not built: rays pass through height maps
         case SH_PLANE: { // Plane::intersects_segment
             V3 n(s.p.x, s.p.y, s.p.z);
             V3 segment = from - to;

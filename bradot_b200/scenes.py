@@ -14,7 +14,7 @@ import struct
 
 import numpy as np
 
-SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONVEX, SHAPE_CONCAVE = range(8)
+SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONVEX, SHAPE_CONCAVE, SHAPE_HEIGHTMAP = range(9)
 MODE_STATIC, MODE_KINEMATIC, MODE_RIGID, MODE_RIGID_LINEAR = range(4)
 JOINT_PIN, JOINT_HINGE = 0, 1
 
@@ -746,6 +746,21 @@ def terrain_faces(n=12, size=8.0, height=0.6, seed=3):
             faces.append((a, b, c))        # winding: the reference's face normal (v0 - v2) x (v0 - v1) points up, the solid side is below
             faces.append((a, c, d))
     return np.array(faces, np.float32).reshape(-1, 3, 3)
+
+
+def heightmap_pile(n=5, seed=12):
+    """terrain_pile() with a HeightMapShape3D (13 x 13 heights, one unit apart) in place of the triangle mesh."""
+    sc = terrain_pile(n, seed)
+    rng = np.random.default_rng(seed + 1)
+    w = d = 13
+    gx, gz = np.meshgrid(np.arange(w) - 6.0, np.arange(d) - 6.0, indexing="xy")
+    h = (0.5 * np.sin(gx * 0.9) * np.cos(gz * 0.7) + 0.15 * rng.uniform(-1, 1, gx.shape)).astype(np.float32)
+    verts = np.zeros((w * d, 3), np.float32)
+    verts[:, 0] = h.reshape(-1)               # row by row: index = z * width + x
+    hm = sc.add_shape(SHAPE_HEIGHTMAP, (w, d, float(h.min()) - 0.1, float(h.max()) + 0.1), verts=verts)
+    sc.bodies["shape"][1] = hm                # body 1 was the triangle-mesh terrain
+    sc.name = "heightmap_pile"
+    return sc
 
 
 def terrain_pile(n=5, seed=11, backface=False):

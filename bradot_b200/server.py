@@ -37,7 +37,7 @@ _STATE_WIDTH = {0: 12, 1: 3, 2: 3, 3: 1, 4: 1}
 
 EXPORTS = [
     "bpc_create", "bpc_destroy", "bpc_last_error", "bpc_set_stream", "bpc_space_create", "bpc_space_set_param",
-    "bpc_shape_create", "bpc_shape_create_convex", "bpc_shape_create_concave", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
+    "bpc_shape_create", "bpc_shape_create_convex", "bpc_shape_create_concave", "bpc_shape_create_heightmap", "bpc_bodies_create", "bpc_bodies_write", "bpc_bodies_read",
     "bpc_body_count", "bpc_joints_create", "bpc_step", "bpc_synchronize", "bpc_get_stats", "bpc_pair_count",
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
     "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
@@ -90,6 +90,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_shape_create.argtypes = [vp, ci, vp]
     lib.bpc_shape_create_convex.argtypes = [vp, vp, ci, vp, vp, ci, vp, ci, vp, ci]
     lib.bpc_shape_create_concave.argtypes = [vp, vp, ci, ci, vp, ci, vp]
+    lib.bpc_shape_create_heightmap.argtypes = [vp, vp, ci, ci, cf, cf]
     lib.bpc_bodies_create.argtypes = [vp, vp, ci]
     lib.bpc_bodies_write.argtypes = [vp, ci, ci, ci, vp]
     lib.bpc_bodies_read.argtypes = [vp, ci, ci, ci, vp]
@@ -223,6 +224,11 @@ class PhysicsServerCUDA:
         nr = None if normals is None else np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
         return self._check(self.lib.bpc_shape_create_concave(self.ctx, _ptr(f), len(f), 1 if backface_collision else 0, None if b is None else _ptr(b),
                                                              0 if b is None else len(b), None if nr is None else _ptr(nr)))
+
+    def heightmap_shape_create(self, heights, width, depth, min_height, max_height):
+        h = np.ascontiguousarray(heights, np.float32).reshape(-1)
+        assert len(h) == width * depth
+        return self._check(self.lib.bpc_shape_create_heightmap(self.ctx, _ptr(h), int(width), int(depth), ctypes.c_float(min_height), ctypes.c_float(max_height)))
 
     # -- bodies -------------------------------------------------------------------------------
     def bodies_create(self, records):
@@ -497,7 +503,10 @@ class PhysicsServerCUDA:
             sp = self.space_create()
             self.space_set_param(sp, SPACE_PARAM_SOLVER_ITERATIONS, sc.iterations + k * getattr(sc, "iter_step", 0))
         for i, s in enumerate(sc.shapes):
-            if s["type"] == scenes.SHAPE_CONCAVE:
+            if s["type"] == scenes.SHAPE_HEIGHTMAP:     # p = (width, depth, min height, max height); the heights are the x of its vertices
+                hs = sc.verts[int(s["vert_ofs"]):int(s["vert_ofs"]) + int(s["vert_cnt"]), 0]
+                self.heightmap_shape_create(hs, int(s["p"][0]), int(s["p"][1]), float(s["p"][2]), float(s["p"][3]))
+            elif s["type"] == scenes.SHAPE_CONCAVE:
                 tree = (meshes or {}).get(("concave", i))
                 faces = sc.verts[int(s["vert_ofs"]):int(s["vert_ofs"]) + int(s["vert_cnt"])]
                 self.concave_polygon_shape_create(faces, s["p"][0] != 0, None if tree is None else tree[0], None if tree is None else tree[1])

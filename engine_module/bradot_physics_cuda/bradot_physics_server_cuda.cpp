@@ -39,6 +39,7 @@ RID BradotPhysicsServerCUDA::box_shape_create() { MAKE_SHAPE(SHAPE_BOX) }
 RID BradotPhysicsServerCUDA::capsule_shape_create() { MAKE_SHAPE(SHAPE_CAPSULE) }
 RID BradotPhysicsServerCUDA::convex_polygon_shape_create() { MAKE_SHAPE(SHAPE_CONVEX_POLYGON) }
 RID BradotPhysicsServerCUDA::concave_polygon_shape_create() { MAKE_SHAPE(SHAPE_CONCAVE_POLYGON) }
+RID BradotPhysicsServerCUDA::heightmap_shape_create() { MAKE_SHAPE(SHAPE_HEIGHTMAP) }
 
 void BradotPhysicsServerCUDA::shape_set_data(RID p_shape, const Variant &p_data) {
 	Shape *shape = shape_owner.get_or_null(p_shape);
@@ -140,6 +141,25 @@ int BradotPhysicsServerCUDA::_shape_handle(Shape *p_shape) {
 				f.push_back(v.z);
 			}
 			p_shape->handle = bpc_shape_create_concave(ctx, f.ptr(), faces.size() / 3, bool(d.get("backface_collision", false)) ? 1 : 0, nullptr, 0, nullptr);
+		} break;
+		case SHAPE_HEIGHTMAP: {
+			// {"width", "depth", "heights" (PackedFloat32Array), optionally "min_height" / "max_height"} (P3D/bradot_shape_3d.cpp:2180-2250)
+			Dictionary d = p_shape->data;
+			ERR_FAIL_COND_V(!d.has("width") || !d.has("depth") || !d.has("heights"), -1);
+			int w = d["width"], dp = d["depth"];
+			PackedFloat32Array hs = d["heights"];
+			ERR_FAIL_COND_V(w <= 0 || dp <= 0 || hs.size() != w * dp, -1);
+			float mn = 0.f, mx = 0.f;
+			if (d.has("min_height") && d.has("max_height")) {
+				mn = d["min_height"];
+				mx = d["max_height"];
+			} else {
+				for (int i = 0; i < hs.size(); i++) {
+					mn = MIN(mn, hs[i]);
+					mx = MAX(mx, hs[i]);
+				}
+			}
+			p_shape->handle = bpc_shape_create_heightmap(ctx, hs.ptr(), w, dp, mn, mx);
 		} break;
 		default:
 			ERR_FAIL_V_MSG(-1, "BradotPhysicsCUDA: unsupported shape type.");

@@ -257,6 +257,7 @@ public:
 	virtual RID capsule_shape_create() override;
 	virtual RID convex_polygon_shape_create() override;
 	virtual RID concave_polygon_shape_create() override;
+	virtual RID heightmap_shape_create() override;
 	virtual void shape_set_data(RID p_shape, const Variant &p_data) override;
 	virtual ShapeType shape_get_type(RID p_shape) const override;
 	virtual Variant shape_get_data(RID p_shape) const override;

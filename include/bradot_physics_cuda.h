@@ -132,10 +132,14 @@ int bpc_shape_create_convex(bpc_context *ctx, const float *verts, int n_verts, c
  * floats (box position, box size, left, right, face index or -1) in pre-order, normals = n_faces x 3 -- what the tests do with
  * the reference's own tree, so that faces are met in its order.  Against a mesh: the step (all four body shapes), intersect_shape,
  * collide_shape, rest_info, body_test_motion's recovery and rest steps, intersect_ray (nearest face; a point is never inside a
- * mesh), cast_motion and the cast of body_test_motion (GJK distance face by face).  Not built: HeightMapShape3D; continuous
- * collision detection against a mesh. */
+ * mesh), cast_motion and the cast of body_test_motion (GJK distance face by face). */
 int bpc_shape_create_concave(bpc_context *ctx, const float *faces, int n_faces, int backface_collision, const float *bvh_nodes, int n_nodes,
                              const float *normals);
+/* HeightMapShape3D (P3D/bradot_shape_3d.cpp:2028-2078, 2159-2178): width x depth heights row by row (z major), one unit apart,
+ * centred on the shape's origin, solid on both sides; static bodies only.  Collides in the step and answers intersect_shape,
+ * collide_shape, rest_info, cast_motion and body_test_motion like a triangle mesh; rays pass through it (the reference's grid
+ * walk for segments is not built). */
+int bpc_shape_create_heightmap(bpc_context *ctx, const float *heights, int width, int depth, float min_height, float max_height);
 
 /* ---- bodies */
 int bpc_bodies_create(bpc_context *ctx, const bpc_body_desc *descs, int n); /* returns first body index */

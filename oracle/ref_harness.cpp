@@ -946,6 +946,20 @@ int main(int argc, char **argv) {
 				dct["backface_collision"] = s.p[0] != 0.f;
 				ps->shape_set_data(sh, dct);
 			} break;
+			case PhysicsServer3D::SHAPE_HEIGHTMAP: { // p = (width, depth, min height, max height); heights = x of its vertices
+				sh = ps->heightmap_shape_create();
+				PackedFloat32Array hs;
+				for (uint32_t k = 0; k < s.vert_cnt; k++) {
+					hs.push_back(sverts[(s.vert_ofs + k) * 3]);
+				}
+				Dictionary dct;
+				dct["width"] = (int)s.p[0];
+				dct["depth"] = (int)s.p[1];
+				dct["heights"] = hs;
+				dct["min_height"] = s.p[2];
+				dct["max_height"] = s.p[3];
+				ps->shape_set_data(sh, dct);
+			} break;
 			default:
 				fprintf(stderr, "unsupported shape type %u\n", s.type);
 				return 2;

@@ -411,3 +411,13 @@ def test_static_triangle_meshes_match_the_reference():
     counts, bodies = ps.intersect_shapes([probe, probe], np.stack([np.concatenate([eye, [0.0, 3.0, 0.0]]), np.concatenate([eye, [0.0, 0.0, 0.0]])]).astype(np.float32), max_results=8)
     assert 1 not in bodies[0, :counts[0]] and 1 in bodies[1, :counts[1]]
     ps.finish()
+
+
+def test_height_maps_match_the_reference():
+    """HeightMapShape3D (bradot_shape_3d.cpp:2028-2078: the cells under the body's box, two faces each) under spheres, boxes,
+    capsules and hulls, teacher-forced: pair list, colliding pairs and contact counts equal, contacts 1e-5, body state 1e-4."""
+    _need_oracle()
+    sc = scenes.heightmap_pile()
+    w = parity.teacher_forced(sc, 151, [20, 45, 70, 100, 150])
+    assert w["colliding"] > 20 and w["contacts"] > 40, w
+    assert w["contact"] < CONTACT_TOL and w["state"] < 1e-4, w
