@@ -165,3 +165,74 @@ def test_mixed_pile_is_bit_reproducible_and_every_awake_body_is_stepped():
             assert ia.shape == ib.shape and np.array_equal(ia, ib) and np.array_equal(pa, pb) and np.array_equal(ca, cb), s
     a.finish()
     b.finish()
+
+
+def test_edge_cases_of_the_round_2_entry_points():
+    """Empty batches, bad handles and refused combinations of the entry points added in round 2 answer with an error message
+    (or with nothing), never with a crash or a silent ignore."""
+    sc = scenes.spheres_container(2, 2, 2, half=1.5)
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc)
+    ps.step(sc.dt)
+    eye = np.array([1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 1, 0], np.float32)
+    probe = ps.sphere_shape_create(0.3)
+    # empty batches
+    assert len(ps.rest_infos(np.zeros(0, np.int32), np.zeros((0, 12), np.float32))) == 0
+    fr, info = ps.cast_motions(np.zeros(0, np.int32), np.zeros((0, 12), np.float32), np.zeros((0, 3), np.float32))
+    assert len(fr) == 0 and len(info) == 0
+    assert len(ps.bodies_test_motion(np.zeros(0, server.MOTION_PARAMS_DT))) == 0
+    assert len(ps.area_events()) == 0
+    ps.set_query_exclude([])
+    # a zero motion: nothing in the way, fractions (1, 1)
+    fr, info = ps.cast_motions([probe], eye, [[0, 0, 0]])
+    assert fr[0, 0] == 1 and fr[0, 1] == 1
+    # bad handles
+    with pytest.raises(server.PhysicsError):
+        ps.rest_infos([9999], eye)
+    with pytest.raises(server.PhysicsError):
+        ps.set_query_exclude([10 ** 6])
+    bad = np.zeros(1, server.MOTION_PARAMS_DT)
+    bad["body"] = 10 ** 6
+    with pytest.raises(server.PhysicsError):
+        ps.bodies_test_motion(bad)
+    bad["body"], bad["max_collisions"] = 5, 33
+    with pytest.raises(server.PhysicsError):
+        ps.bodies_test_motion(bad)
+    # areas: unknown space, world boundary as area shape, out-of-range override mode, writing a destroyed area
+    ar = np.zeros(1, scenes.AREA_DT)
+    ar["xf"], ar["shape_xf"], ar["shape"], ar["layer"], ar["mask"] = scenes.IDENT12, scenes.IDENT12, probe, 1, 1
+    ar["space"] = 7
+    with pytest.raises(server.PhysicsError):
+        ps.areas_create(ar)
+    ar["space"], ar["shape"] = 0, int(sc.bodies["shape"][0])          # body 0 is a world boundary
+    with pytest.raises(server.PhysicsError):
+        ps.areas_create(ar)
+    ar["shape"], ar["gravity_mode"] = probe, 9
+    with pytest.raises(server.PhysicsError):
+        ps.areas_create(ar)
+    ar["gravity_mode"] = 3
+    first = ps.areas_create(ar)
+    ps.step(sc.dt)
+    ps.areas_destroy([first])
+    with pytest.raises(server.PhysicsError):
+        ps.areas_write(first, ar)
+    ps.areas_destroy([first])                                          # twice: nothing happens
+    ps.step(sc.dt)
+    # meshes: only static bodies may carry one; an empty mesh and a tree that is not one are refused
+    tri = np.array([[[0, 0, 0], [1, 0, 1], [1, 0, 0]]], np.float32)
+    mesh = ps.concave_polygon_shape_create(tri)
+    body = sc.bodies[-1:].copy()
+    body["shape"], body["mode"] = mesh, scenes.MODE_RIGID
+    with pytest.raises(server.PhysicsError):
+        ps.bodies_create(body)
+    body["mode"] = scenes.MODE_STATIC
+    ps.bodies_create(body)
+    with pytest.raises(server.PhysicsError):
+        ps.concave_polygon_shape_create(np.zeros((0, 9), np.float32))
+    with pytest.raises(server.PhysicsError):
+        ps.concave_polygon_shape_create(tri, bvh=np.array([[0, 0, 0, 1, 0, 1, 5, 7, -1]], np.float32), normals=np.array([[0, 1, 0]], np.float32))
+    with pytest.raises(server.PhysicsError):
+        ps.heightmap_shape_create(np.zeros(1, np.float32), 1, 1, 0.0, 0.0)
+    ps.step(sc.dt)
+    assert np.all(np.isfinite(ps.bodies_read(server.FIELD_TRANSFORM)))
+    ps.finish()
