@@ -532,6 +532,17 @@ extern "C" int bpc_body_count(bpc_context *ctx) { return ctx ? (int)ctx->n_bodie
 
 // ---------------------------------------------------------------------------------------------- joints
 static void joint_defaults(JointRec &j) {
+    if (j.type == BPC_JOINT_CONE_TWIST) {
+        // ConeTwistJointParam order: swing span, twist span, bias, softness, relaxation; [5] is the second swing span, which
+        // cone_twist_joint_set_param(SWING_SPAN) sets together with the first (bradot_cone_twist_joint_3d.cpp:278-281) and which
+        // an untouched joint has at 0 beside tau / 8 (bradot_cone_twist_joint_3d.h:80-86)
+        if (j.flags & JF_HAS_PARAMS) return;
+        memset(j.prm, 0, sizeof(j.prm));
+        j.prm[0] = (float)(6.2831853071795864769252867666 / 8.0);
+        j.prm[2] = 0.3f;
+        j.prm[4] = 1.0f;
+        return;
+    }
     if (j.flags & JF_HAS_PARAMS) return;
     memset(j.prm, 0, sizeof(j.prm));
     if (j.type == BPC_JOINT_PIN) { // bradot_pin_joint_3d.h: m_tau 0.3, m_damping 1, m_impulseClamp 0
@@ -558,7 +569,7 @@ static int joint_from_desc(bpc_context *ctx, const bpc_joint_desc &d, JointRec &
     static_assert(sizeof(JointRec) == sizeof(bpc_joint_desc), "JointRec mirrors bpc_joint_desc");
     if (d.body_a >= ctx->n_bodies || d.body_b >= ctx->n_bodies || d.body_a == d.body_b || ctx->h_dead[d.body_a] || ctx->h_dead[d.body_b])
         return fail(ctx, "joint: invalid body");
-    if (d.type > BPC_JOINT_HINGE) return fail(ctx, "joint: unsupported joint type (pin, hinge)");
+    if (d.type > BPC_JOINT_CONE_TWIST) return fail(ctx, "joint: unsupported joint type (pin, hinge, cone twist)");
     if (d.priority > 15) return fail(ctx, "joint: solver priority above 15");
     memcpy(&j, &d, sizeof(JointRec));
     j.flags &= ~JF_DEAD;

@@ -574,6 +574,90 @@ __global__ void __launch_bounds__(128) k_joint_setup(JsArgs a) {
         nrm[1] = V3(0.f, 1.f, 0.f);
         nrm[2] = V3(0.f, 0.f, 1.f);
         s.prm = make_float4(jr.prm[0], jr.prm[1], jr.prm[2], 0.f); // bias (tau), damping, impulse clamp
+    } else if (jr.type == 2) {
+        // cone twist (joints/bradot_cone_twist_joint_3d.cpp:67-203): the three linear rows of a hinge, then where the swing
+        // (the ellipse of the two swing spans) and the twist stand against their limits
+        V3 relPos = pivB - pivA;
+        if (is_zero_approx(length_squared(relPos))) nrm[0] = V3(1.0f, 0.f, 0.f);
+        else nrm[0] = normalized(relPos);
+        plane_space(nrm[0], nrm[1], nrm[2]);
+        const float swingSpan1 = jr.prm[0], swingSpan2 = jr.prm[5], twistSpan = jr.prm[1], limitSoftness = jr.prm[3];
+        M3 iwA(f4v(mwa.i0), f4v(mwa.i1), f4v(mwa.i2)), iwB(f4v(mwb.i0), f4v(mwb.i1), f4v(mwb.i2));
+        V3 b1Axis1 = xform(XA.b, V3(jr.fa[0], jr.fa[3], jr.fa[6])), b1Axis2, b1Axis3;
+        V3 b2Axis1 = xform(XB.b, V3(jr.fb[0], jr.fb[3], jr.fb[6]));
+        float swing1 = 0.f, swing2 = 0.f, swx = 0.f, swy = 0.f, fact;
+        const float thresh = 10.f;
+        if (swingSpan1 >= 0.05f) {
+            b1Axis2 = xform(XA.b, V3(jr.fa[1], jr.fa[4], jr.fa[7]));
+            swx = dot(b2Axis1, b1Axis1);
+            swy = dot(b2Axis1, b1Axis2);
+            swing1 = atan2fast(swy, swx);
+            fact = (swy * swy + swx * swx) * thresh * thresh;
+            fact = fact / (fact + 1.0f);
+            swing1 *= fact;
+        }
+        if (swingSpan2 >= 0.05f) {
+            b1Axis3 = xform(XA.b, V3(jr.fa[2], jr.fa[5], jr.fa[8]));
+            swx = dot(b2Axis1, b1Axis1);
+            swy = dot(b2Axis1, b1Axis3);
+            swing2 = atan2fast(swy, swx);
+            fact = (swy * swy + swx * swx) * thresh * thresh;
+            fact = fact / (fact + 1.0f);
+            swing2 *= fact;
+        }
+        float RMaxAngle1Sq = 1.0f / (swingSpan1 * swingSpan1);
+        float RMaxAngle2Sq = 1.0f / (swingSpan2 * swingSpan2);
+        float EllipseAngle = fabsf(swing1 * swing1) * RMaxAngle1Sq + fabsf(swing2 * swing2) * RMaxAngle2Sq;
+        V3 swingAxis, twistAxis;
+        float kSwing = 0.f, kTwist = 0.f, swingCorrection = 0.f, twistCorrection = 0.f;
+        if (EllipseAngle > 1.0f) {
+            swingCorrection = EllipseAngle - 1.0f;
+            flags |= 16u; // m_solveSwingLimit
+            swingAxis = cross(b2Axis1, b1Axis2 * dot(b2Axis1, b1Axis2) + b1Axis3 * dot(b2Axis1, b1Axis3));
+            swingAxis = normalized(swingAxis);
+            float swingAxisSign = (dot(b2Axis1, b1Axis1) >= 0.0f) ? 1.0f : -1.0f;
+            swingAxis *= swingAxisSign;
+            kSwing = 1.0f / (dot(swingAxis, xform_inv(iwA, swingAxis)) + dot(swingAxis, xform_inv(iwB, swingAxis)));
+        }
+        if (twistSpan >= 0.f) {
+            V3 b2Axis22 = xform(XB.b, V3(jr.fb[1], jr.fb[4], jr.fb[7]));
+            // Quaternion(b2Axis1, b1Axis1), the shortest arc (core/math/quaternion.h:144-162), and its xform (:91-98)
+            V3 qc = cross(b2Axis1, b1Axis1);
+            float qd = dot(b2Axis1, b1Axis1);
+            V3 qu;
+            float qw;
+            if (qd < -1.0f + (float)BPC_CMP_EPSILON) {
+                qu = V3(0.f, 1.f, 0.f);
+                qw = 0.f;
+            } else {
+                float sq = sqrtf((1.0f + qd) * 2.0f);
+                float rs = 1.0f / sq;
+                qu = V3(qc.x * rs, qc.y * rs, qc.z * rs);
+                qw = sq * 0.5f;
+            }
+            V3 uv = cross(qu, b2Axis22);
+            V3 TwistRef = b2Axis22 + ((uv * qw) + cross(qu, uv)) * 2.0f;
+            float twist = atan2fast(dot(TwistRef, b1Axis3), dot(TwistRef, b1Axis2));
+            float lockedFreeFactor = (twistSpan > 0.05f) ? limitSoftness : 0.f;
+            if (twist <= -twistSpan * lockedFreeFactor) {
+                twistCorrection = -(twist + twistSpan);
+                flags |= 32u; // m_solveTwistLimit
+                twistAxis = (b2Axis1 + b1Axis1) * 0.5f;
+                twistAxis = normalized(twistAxis);
+                twistAxis *= -1.0f;
+                kTwist = 1.0f / (dot(twistAxis, xform_inv(iwA, twistAxis)) + dot(twistAxis, xform_inv(iwB, twistAxis)));
+            } else if (twist > twistSpan * lockedFreeFactor) {
+                twistCorrection = (twist - twistSpan);
+                flags |= 32u;
+                twistAxis = (b2Axis1 + b1Axis1) * 0.5f;
+                twistAxis = normalized(twistAxis);
+                kTwist = 1.0f / (dot(twistAxis, xform_inv(iwA, twistAxis)) + dot(twistAxis, xform_inv(iwB, twistAxis)));
+            }
+        }
+        s.axis_a = v4(swingAxis, kSwing);
+        s.axis_b = v4(twistAxis, kTwist);
+        s.lim = make_float4(swingCorrection, 0.f, twistCorrection, 0.f); // corrections; accumulated swing / twist limit impulses
+        s.prm = make_float4(0.3f, jr.prm[4], jr.prm[2], 0.f);             // tau (fixed, :208), relaxation, bias
     } else {
         V3 relPos = pivB - pivA;
         if (is_zero_approx(length_squared(relPos))) nrm[0] = V3(1.0f, 0.f, 0.f);
@@ -665,6 +749,47 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
             V3 iv = normal * impulse;
             if (dynA) apply_impulse(A, iv, pA);
             if (dynB) apply_impulse(B, -iv, pB);
+        }
+    } else if (type == 2) { // cone twist (joints/bradot_cone_twist_joint_3d.cpp:205-279)
+        V3 vel1 = A.lin + cross(A.ang, pA - A.com);
+        V3 vel2 = B.lin + cross(B.ang, pB - B.com);
+        V3 vel = vel1 - vel2;
+        for (int i = 0; i < 3; i++) {
+            V3 normal = f4v(rows[i]);
+            float jinv = rows[i].w;
+            float rel_vel = dot(normal, vel);
+            float depth = -dot(dpos, normal);
+            float impulse = depth * tau / a.dt * jinv - rel_vel * jinv;
+            V3 iv = normal * impulse;
+            if (dynA) apply_impulse(A, iv, pA);
+            if (dynB) apply_impulse(B, -iv, pB);
+        }
+        const float relaxation = js.prm.y, bias = js.prm.z;
+        // get_angular_velocity() returns by value (bradot_body_3d.h:216): both limits see the velocities as the linear rows left them
+        const V3 angVelA = A.ang, angVelB = B.ang;
+        if (flags & 16u) {
+            V3 swingAxis = f4v(js.axis_a);
+            float amplitude = (dot(angVelB - angVelA, swingAxis) * relaxation * relaxation + js.lim.x * (1.0f / a.dt) * bias);
+            float impulseMag = amplitude * js.axis_a.w;
+            float temp = a.jsetup[inf.w].lim.y;
+            float acc = fmaxf(temp + impulseMag, 0.0f);
+            a.jsetup[inf.w].lim.y = acc;
+            impulseMag = acc - temp;
+            V3 impulse = swingAxis * impulseMag;
+            if (dynA) A.ang += xform(A.iinv, impulse);
+            if (dynB) B.ang += xform(B.iinv, -impulse);
+        }
+        if (flags & 32u) {
+            V3 twistAxis = f4v(js.axis_b);
+            float amplitude = (dot(angVelB - angVelA, twistAxis) * relaxation * relaxation + js.lim.z * (1.0f / a.dt) * bias);
+            float impulseMag = amplitude * js.axis_b.w;
+            float temp = a.jsetup[inf.w].lim.w;
+            float acc = fmaxf(temp + impulseMag, 0.0f);
+            a.jsetup[inf.w].lim.w = acc;
+            impulseMag = acc - temp;
+            V3 impulse = twistAxis * impulseMag;
+            if (dynA) A.ang += xform(A.iinv, impulse);
+            if (dynB) B.ang += xform(B.iinv, -impulse);
         }
     } else { // hinge: one velocity sample for the three linear rows
         V3 vel1 = A.lin + cross(A.ang, pA - A.com);

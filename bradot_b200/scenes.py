@@ -16,7 +16,7 @@ import numpy as np
 
 SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONVEX, SHAPE_CONCAVE, SHAPE_HEIGHTMAP = range(9)
 MODE_STATIC, MODE_KINEMATIC, MODE_RIGID, MODE_RIGID_LINEAR = range(4)
-JOINT_PIN, JOINT_HINGE = 0, 1
+JOINT_PIN, JOINT_HINGE, JOINT_CONE_TWIST = 0, 1, 2
 
 SHAPE_DT = np.dtype([("type", "<u4"), ("p", "<f4", 4), ("vert_ofs", "<u4"), ("vert_cnt", "<u4"), ("pad", "<u4")])
 BODY_DT = np.dtype([
@@ -497,13 +497,15 @@ def pushed(n=24):
     return sc
 
 
-def hanging_chains(n_chains=12, chain_len=5, seed=5):
+def hanging_chains(n_chains=12, chain_len=5, seed=5, cone_twist=False):
     """Joint parameters, hinge limits and motors, solver priorities: chains of boxes hanging from static anchors in empty
     space (the links are on no collision layer, so every island consists of joints only).  Chain c: links joined
     alternately by hinge and pin, the top link pinned to the anchor.  Hinges with an even index use a limit of
     [-0.35, 0.5] rad, every third one also runs a motor; pins with an index divisible by 3 carry their own bias / damping /
     impulse clamp.  All joints of chain c have solver priority 2 when c % 3 == 2 (one priority per island: the reference
-    compacts its island lists in place between priority rounds, which a mixed island would not survive as a dump)."""
+    compacts its island lists in place between priority rounds, which a mixed island would not survive as a dump).
+    cone_twist: the pins between links become cone-twist joints (ConeTwistJointParam order: swing span, twist span, bias,
+    softness, relaxation) with spans small enough for both limits to engage; every third one keeps the untouched defaults."""
     sc = Scene(name="hanging_chains_%d" % n_chains)
     anchor = sc.add_shape(SHAPE_BOX, (0.1, 0.1, 0.1))
     link = sc.add_shape(SHAPE_BOX, (0.1, 0.3, 0.15))
@@ -542,6 +544,18 @@ def hanging_chains(n_chains=12, chain_len=5, seed=5):
                     prm[0] = 0.45                          # bias
                 sc.add_joints(1, type=JOINT_HINGE, body_a=first + k, body_b=first + k + 1, flags=flags, fa=fa, fb=fb, params=prm, priority=prio)
                 hinge_i += 1
+            elif cone_twist:
+                flags, prm = JOINT_NO_COLLIDE, np.zeros(8, np.float32)
+                if pin_i % 3 != 2:
+                    flags |= JOINT_HAS_PARAMS
+                    prm[0:5] = (0.3 + 0.1 * (pin_i % 2), 0.25, 0.3 + 0.1 * (pin_i % 3), 0.8, 0.9 + 0.1 * (pin_i % 2))
+                    prm[5] = prm[0]              # the second swing span: set_param(SWING_SPAN) writes both
+                ca, cb = fa.copy(), fb.copy()
+                ang = 0.2 * (pin_i % 4)          # the frames are turned about z and y, so that swing and twist axes are not body axes
+                ca[0], ca[1], ca[3], ca[4] = np.cos(ang), -np.sin(ang), np.sin(ang), np.cos(ang)
+                cb[0], cb[2], cb[6], cb[8] = np.cos(ang), np.sin(ang), -np.sin(ang), np.cos(ang)
+                sc.add_joints(1, type=JOINT_CONE_TWIST, body_a=first + k, body_b=first + k + 1, flags=flags, fa=ca, fb=cb, params=prm, priority=prio)
+                pin_i += 1
             else:
                 flags, prm = JOINT_NO_COLLIDE, PIN_DEFAULTS.copy()
                 if pin_i % 3 == 0:

@@ -6,7 +6,7 @@
 // Implemented by hand: what a scene of RigidBody3D / StaticBody3D nodes needs -- spaces (create, activate, parameters, free),
 // world-boundary / sphere / box / capsule / convex shapes, bodies with one shape (every setter also after the body is in a
 // space; state-sync and force-integration callbacks; PhysicsDirectBodyState3D; impulses, forces, constant forces; axis
-// locks; collision exceptions; free), pin and hinge joints with their parameters, flags and solver priority, step, stats,
+// locks; collision exceptions; free), pin, hinge and cone-twist joints with their parameters, flags and solver priority, step, stats,
 // PhysicsDirectSpaceState3D queries.  Every other pure virtual of the interface gets a generated default override
 // (engine_module/gen_stubs.py) that logs once and returns the type's default, which is how the reference answers an
 // invalid RID.
@@ -159,6 +159,9 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		// HingeJointParam order; defaults of modules/bradot_physics_3d/joints/bradot_hinge_joint_3d.h:73-88
 		real_t hinge_params[HINGE_JOINT_MAX] = { 0.3, -Math_PI, Math_PI, 0.3, 0.9, 1.0, 0.0, 0.0 };
 		bool hinge_flags[HINGE_JOINT_FLAG_MAX] = { false, false };
+		// ConeTwistJointParam order, then the second swing span (bradot_cone_twist_joint_3d.h:80-86: tau / 8 and 0 until
+		// SWING_SPAN is set, which writes both)
+		real_t cone_params[CONE_TWIST_MAX + 1] = { Math_TAU / 8.0, 0.0, 0.3, 0.0, 1.0, 0.0 };
 		bool pending = false;
 		int handle = -1;
 	};
@@ -369,6 +372,9 @@ public:
 	virtual real_t hinge_joint_get_param(RID p_joint, HingeJointParam p_param) const override;
 	virtual void hinge_joint_set_flag(RID p_joint, HingeJointFlag p_flag, bool p_enabled) override;
 	virtual bool hinge_joint_get_flag(RID p_joint, HingeJointFlag p_flag) const override;
+	virtual void joint_make_cone_twist(RID p_joint, RID p_body_A, const Transform3D &p_local_frame_A, RID p_body_B, const Transform3D &p_local_frame_B) override;
+	virtual void cone_twist_joint_set_param(RID p_joint, ConeTwistJointParam p_param, real_t p_value) override;
+	virtual real_t cone_twist_joint_get_param(RID p_joint, ConeTwistJointParam p_param) const override;
 	// lifecycle
 	virtual void free(RID p_rid) override;
 	virtual void set_active(bool p_active) override;

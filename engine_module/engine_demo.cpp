@@ -278,6 +278,13 @@ int main(int argc, char **argv) {
 					ps->pin_joint_set_param(jr, (PhysicsServer3D::PinJointParam)k, j.params[k]);
 				}
 			}
+		} else if (j.type == 2) {
+			ps->joint_make_cone_twist(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
+			if (j.flags & 8) {
+				for (int k = 0; k < (int)PhysicsServer3D::CONE_TWIST_MAX; k++) {
+					ps->cone_twist_joint_set_param(jr, (PhysicsServer3D::ConeTwistJointParam)k, j.params[k]);
+				}
+			}
 		} else {
 			ps->joint_make_hinge(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
 			if (j.flags & 8) {

@@ -21,7 +21,7 @@ typedef struct bpc_context bpc_context;
 
 enum { BPC_SHAPE_WORLD_BOUNDARY = 0, BPC_SHAPE_SPHERE = 2, BPC_SHAPE_BOX = 3, BPC_SHAPE_CAPSULE = 4, BPC_SHAPE_CONVEX_POLYGON = 6 };
 enum { BPC_BODY_MODE_STATIC = 0, BPC_BODY_MODE_KINEMATIC = 1, BPC_BODY_MODE_RIGID = 2, BPC_BODY_MODE_RIGID_LINEAR = 3 };
-enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1 };
+enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1, BPC_JOINT_CONE_TWIST = 2 };
 
 /* Bulk body description; one record per body.  Same layout as the record of the neutral scene
  * file (bradot_b200/scenes.py BODY_DT).  Replaces the per-body call sequence body_create /
@@ -45,12 +45,16 @@ typedef struct bpc_body_desc {
 typedef struct bpc_joint_desc {
     /* flags: bit0 the two bodies do not collide with each other (joint_disable_collisions_between_bodies), bit1 hinge
      * HINGE_JOINT_FLAG_USE_LIMIT, bit2 hinge HINGE_JOINT_FLAG_ENABLE_MOTOR, bit3 `params` holds values (otherwise the
-     * reference's defaults: pin 0.3 / 1 / 0, hinge P3D/joints/bradot_hinge_joint_3d.h:73-88) */
+     * reference's defaults: pin 0.3 / 1 / 0, hinge P3D/joints/bradot_hinge_joint_3d.h:73-88, cone twist
+     * P3D/joints/bradot_cone_twist_joint_3d.h:80-86) */
     uint32_t type, body_a, body_b, flags;
-    float frame_a[12], frame_b[12]; /* pin: origins only (local anchors); hinge: local frames */
+    float frame_a[12], frame_b[12]; /* pin: origins only (local anchors); hinge, cone twist: local frames */
     /* pin: PinJointParam order (bias, damping, impulse clamp; P3D/joints/bradot_pin_joint_3d.cpp:143-155); hinge:
      * HingeJointParam order (bias, limit upper, limit lower, limit bias, limit softness, limit relaxation, motor target
-     * velocity, motor max impulse; P3D/joints/bradot_hinge_joint_3d.cpp:362-392) */
+     * velocity, motor max impulse; P3D/joints/bradot_hinge_joint_3d.cpp:362-392); cone twist: ConeTwistJointParam order
+     * (swing span, twist span, bias, softness, relaxation; P3D/joints/bradot_cone_twist_joint_3d.cpp:274-296), then in
+     * params[5] the SECOND swing span: cone_twist_joint_set_param(SWING_SPAN) writes both spans, so pass the same value
+     * twice -- except for a joint whose swing span was never set, which has tau / 8 and 0 */
     float params[8];
     uint32_t priority; /* joint_set_solver_priority (P3D/bradot_physics_server_3d.cpp:1376): 0 or 1 = default */
     uint32_t reserved[3];

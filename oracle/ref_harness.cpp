@@ -1025,6 +1025,8 @@ int main(int argc, char **argv) {
 		RID jr = ps->joint_create();
 		if (j.type == 0) {
 			ps->joint_make_pin(jr, w.bodies[j.body_a], Vector3(j.fa[9], j.fa[10], j.fa[11]), w.bodies[j.body_b], Vector3(j.fb[9], j.fb[10], j.fb[11]));
+		} else if (j.type == 2) {
+			ps->joint_make_cone_twist(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		} else {
 			ps->joint_make_hinge(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		}
@@ -1035,6 +1037,10 @@ int main(int argc, char **argv) {
 			if (j.type == 0) {
 				for (int k = 0; k < 3; k++) {
 					ps->pin_joint_set_param(jr, (PhysicsServer3D::PinJointParam)k, j.params[k]);
+				}
+			} else if (j.type == 2) {
+				for (int k = 0; k < (int)PhysicsServer3D::CONE_TWIST_MAX; k++) {
+					ps->cone_twist_joint_set_param(jr, (PhysicsServer3D::ConeTwistJointParam)k, j.params[k]);
 				}
 			} else {
 				for (int k = 0; k < (int)PhysicsServer3D::HINGE_JOINT_MAX; k++) {

@@ -421,3 +421,26 @@ def test_height_maps_match_the_reference():
     w = parity.teacher_forced(sc, 151, [20, 45, 70, 100, 150])
     assert w["colliding"] > 20 and w["contacts"] > 40, w
     assert w["contact"] < CONTACT_TOL and w["state"] < 1e-4, w
+
+
+def test_cone_twist_joints_match_the_reference():
+    """ConeTwistJoint3D (joints/bradot_cone_twist_joint_3d.cpp:67-279: swing ellipse and twist limits with accumulated, clamped
+    impulses, the shortest-arc quaternion for the twist reference): chains whose links alternate hinges and cone-twist joints,
+    teacher-forced with the reference's sweep order, body state after the step within 1e-4; the limits do engage."""
+    _need_oracle()
+    sc = scenes.hanging_chains(cone_twist=True)
+    assert (sc.joints["type"] == scenes.JOINT_CONE_TWIST).sum() >= 20
+    _, dump = parity.run_oracle(sc, 80)
+    w = parity.teacher_forced(sc, 80, [1, 5, 15, 30, 50, 79], dump=dump)
+    assert w["state"] < STATE_TOL, w
+    # the same chains with pins in place of the cone twists swing differently: the limits are at work
+    plain = scenes.hanging_chains(cone_twist=True)
+    plain.joints["type"][plain.joints["type"] == scenes.JOINT_CONE_TWIST] = scenes.JOINT_PIN
+    plain.joints["flags"] &= ~np.uint32(scenes.JOINT_HAS_PARAMS)
+    ps = parity.new_server(plain, dump)
+    parity.load_state(ps, dump, 30)
+    ps.set_solve_order(parity.solve_order(dump, 31))
+    ps.step(sc.dt)
+    av = ps.bodies_read(server.FIELD_ANGULAR_VELOCITY)
+    assert parity.rel_err(av, dump[("bodies", 31)][:, 15:18], 1.0) > 1e-2
+    ps.finish()

@@ -1,0 +1,3 @@
+cd $GRAFT_REPO_ROOT
+python -m pytest tests/test_gpu_features.py -q -m gpu --timeout 1500 -p no:cacheprovider -k "cone_twist or joint_parameters" > gpurun_out/s48_tests.log 2>&1
+tail -30 gpurun_out/s48_tests.log | cut -c1-300
