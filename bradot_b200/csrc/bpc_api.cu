@@ -57,7 +57,7 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
     }
     ctx->except_keys.free_(); ctx->con_list.free_(); ctx->con_color.free_(); ctx->con_sorted.free_(); ctx->con_sorted_alt.free_();
     ctx->con_info.free_(); ctx->con_bin.free_(); ctx->con_sorted_color.free_(); ctx->joint_color.free_(); ctx->report_cap.free_(); ctx->report_ofs.free_(); ctx->report_count.free_(); ctx->reports.free_(); ctx->report_overflow.free_(); ctx->report_overflow_body.free_(); ctx->con_cls.free_(); ctx->bin_tab.free_(); ctx->bin_base.free_(); ctx->body_best.free_(); ctx->body_colmask.free_(); ctx->color_start.free_(); ctx->scontacts.free_();
-    ctx->forced_order.free_(); ctx->forced_level_start.free_(); ctx->forced_keys.free_(); ctx->d_joints.free_();
+    ctx->forced_order.free_(); ctx->forced_level_start.free_(); ctx->forced_keys.free_(); ctx->d_joints.free_(); ctx->d_jext.free_();
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     delete ctx;
 }
@@ -502,6 +502,7 @@ int bpc_flush_tables(bpc_context *ctx) {
     }
     if (ctx->joints_dirty) {
         if (upload(ctx, ctx->d_joints, ctx->h_joints)) return -1;
+        if (!ctx->h_jext.empty() && upload(ctx, ctx->d_jext, ctx->h_jext)) return -1;
         ctx->joints_dirty = false;
     }
     if (ctx->except_dirty) {

@@ -543,6 +543,10 @@ static void joint_defaults(JointRec &j) {
         j.prm[4] = 1.0f;
         return;
     }
+    if (j.type == BPC_JOINT_SLIDER) { // its values are in the long table
+        memset(j.prm, 0, sizeof(j.prm));
+        return;
+    }
     if (j.flags & JF_HAS_PARAMS) return;
     memset(j.prm, 0, sizeof(j.prm));
     if (j.type == BPC_JOINT_PIN) { // bradot_pin_joint_3d.h: m_tau 0.3, m_damping 1, m_impulseClamp 0
@@ -551,6 +555,14 @@ static void joint_defaults(JointRec &j) {
         j.prm[0] = 0.3f; j.prm[1] = (float)-3.14159265358979323846; j.prm[2] = (float)3.14159265358979323846;
         j.prm[3] = 0.3f; j.prm[4] = 0.9f; j.prm[5] = 1.0f; j.prm[6] = 0.0f; j.prm[7] = 0.0f;
     }
+}
+
+// BradotSliderJoint3D's members as constructed (bradot_slider_joint_3d.h:80-110), SliderJointParam order
+static void slider_defaults(float *p) {
+    const float soft = 1.0f, damp = 1.0f, rest = 0.7f;
+    const float v[BPC_SLIDER_PARAMS] = { -1.0f, 1.0f, soft, rest, damp, soft, rest, 0.0f, soft, rest, damp,
+                                         0.0f, 0.0f, soft, rest, damp, soft, rest, 0.0f, soft, rest, damp };
+    memcpy(p, v, sizeof(v));
 }
 
 // collision exceptions are those of the live joints that ask for them
@@ -569,7 +581,7 @@ static int joint_from_desc(bpc_context *ctx, const bpc_joint_desc &d, JointRec &
     static_assert(sizeof(JointRec) == sizeof(bpc_joint_desc), "JointRec mirrors bpc_joint_desc");
     if (d.body_a >= ctx->n_bodies || d.body_b >= ctx->n_bodies || d.body_a == d.body_b || ctx->h_dead[d.body_a] || ctx->h_dead[d.body_b])
         return fail(ctx, "joint: invalid body");
-    if (d.type > BPC_JOINT_CONE_TWIST) return fail(ctx, "joint: unsupported joint type (pin, hinge, cone twist)");
+    if (d.type > BPC_JOINT_SLIDER) return fail(ctx, "joint: unsupported joint type (pin, hinge, cone twist)");
     if (d.priority > 15) return fail(ctx, "joint: solver priority above 15");
     memcpy(&j, &d, sizeof(JointRec));
     j.flags &= ~JF_DEAD;
@@ -587,6 +599,13 @@ extern "C" int bpc_joints_create(bpc_context *ctx, const bpc_joint_desc *descs, 
         if (joint_from_desc(ctx, descs[i], recs[i])) return -1;
     }
     ctx->h_joints.insert(ctx->h_joints.end(), recs.begin(), recs.end());
+    bool want_ext = !ctx->h_jext.empty();
+    for (const JointRec &r : recs) want_ext |= r.type == BPC_JOINT_SLIDER;
+    if (want_ext) {
+        ctx->h_jext.resize(ctx->h_joints.size() * JEXT_STRIDE, 0.f);
+        for (int i = 0; i < n; i++)
+            if (recs[i].type == BPC_JOINT_SLIDER) slider_defaults(&ctx->h_jext[(size_t)(first + i) * JEXT_STRIDE]);
+    }
     rebuild_exceptions(ctx);
     ctx->joints_dirty = true;
     return first;
@@ -642,6 +661,30 @@ extern "C" int bpc_bodies_set_exception(bpc_context *ctx, int body_a, int body_b
     else if (!excepted && have) ctx->h_except_user.erase(it);
     else return 0;
     rebuild_exceptions(ctx);
+    return 0;
+}
+
+static int jext_check(bpc_context *ctx, const char *who, int joint, int first, int n, const void *values) {
+    const char *why = nullptr;
+    if (joint < 0 || (size_t)joint >= ctx->h_joints.size() || (ctx->h_joints[joint].flags & JF_DEAD)) why = ": invalid joint";
+    else if (ctx->h_joints[joint].type != BPC_JOINT_SLIDER) why = ": this joint type has no long parameter table";
+    else if (first < 0 || n < 0 || first + n > BPC_SLIDER_PARAMS || (n > 0 && !values)) why = ": parameter range out of bounds";
+    if (!why) return 0;
+    return fail(ctx, (std::string(who) + why).c_str());
+}
+
+extern "C" int bpc_joint_params_write(bpc_context *ctx, int joint, int first, int n, const float *values) {
+    if (!ctx) return -1;
+    if (jext_check(ctx, "bpc_joint_params_write", joint, first, n, values)) return -1;
+    if (n) memcpy(&ctx->h_jext[(size_t)joint * JEXT_STRIDE + first], values, (size_t)n * sizeof(float));
+    ctx->joints_dirty = true;
+    return 0;
+}
+
+extern "C" int bpc_joint_params_read(bpc_context *ctx, int joint, int first, int n, float *values) {
+    if (!ctx) return -1;
+    if (jext_check(ctx, "bpc_joint_params_read", joint, first, n, values)) return -1;
+    if (n) memcpy(values, &ctx->h_jext[(size_t)joint * JEXT_STRIDE + first], (size_t)n * sizeof(float));
     return 0;
 }
 

@@ -184,6 +184,7 @@ struct JointRec {
 #define JF_ENABLE_MOTOR 4u
 #define JF_HAS_PARAMS 8u
 #define JF_DEAD 0x80000000u
+#define JEXT_STRIDE 24 // long parameter table of a joint (slider: 22 values)
 
 // Per-step joint data written by k_joint_setup (the Jacobian diagonals of BradotJacobianEntry3D and
 // everything about the pivots / axes that stays constant while the solver sweeps).
@@ -222,6 +223,8 @@ struct bpc_context {
     std::vector<uint32_t> h_mindex; // per face: [count, idx...] packed; face_ofs indexes h_mfaces
     std::vector<uint2> h_mfaces;    // (index_ofs, count)
     std::vector<JointRec> h_joints;
+    std::vector<float> h_jext; // JEXT_STRIDE values per joint, present once a joint with a long parameter table exists
+    DevBuf<float> d_jext;
     bool shapes_dirty = true, joints_dirty = true, spaces_dirty = true;
     uint32_t *h_counters = nullptr; // pinned mirror of the device counters of the last step
     uint32_t launches = 0;          // kernels launched by the current / last step

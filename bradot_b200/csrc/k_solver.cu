@@ -513,6 +513,7 @@ __device__ __forceinline__ float jac_diag_inv(const M3 &w2a, const M3 &w2b, V3 r
 struct JsArgs {
     uint32_t n;
     const JointRec *joints;
+    const float *jext; // long parameter tables (sliders), JEXT_STRIDE per joint; null without such joints
     JointSetup *out;
     const BodyXf *xf;
     const BodyMassW *massw;
@@ -658,6 +659,69 @@ __global__ void __launch_bounds__(128) k_joint_setup(JsArgs a) {
         s.axis_b = v4(twistAxis, kTwist);
         s.lim = make_float4(swingCorrection, 0.f, twistCorrection, 0.f); // corrections; accumulated swing / twist limit impulses
         s.prm = make_float4(0.3f, jr.prm[4], jr.prm[2], 0.f);             // tau (fixed, :208), relaxation, bias
+    } else if (jr.type == 3) {
+        // slider (joints/bradot_slider_joint_3d.cpp:74-137, testLinLimits :298-316, testAngLimits :320-337): the rows are the
+        // axes of frame A in the world, the pivot of A is projected on the slider axis, the parameters of the branch that
+        // will run (limit hit or free motion) are chosen here
+        const float *sp = a.jext + (size_t)j * JEXT_STRIDE;
+        M3 fa(V3(jr.fa[0], jr.fa[1], jr.fa[2]), V3(jr.fa[3], jr.fa[4], jr.fa[5]), V3(jr.fa[6], jr.fa[7], jr.fa[8]));
+        M3 fb(V3(jr.fb[0], jr.fb[1], jr.fb[2]), V3(jr.fb[3], jr.fb[4], jr.fb[5]), V3(jr.fb[6], jr.fb[7], jr.fb[8]));
+        M3 ba = XA.b * fa, bb = XB.b * fb; // m_calculatedTransformA / B .basis
+        V3 colA[3] = { V3(ba.r[0].x, ba.r[1].x, ba.r[2].x), V3(ba.r[0].y, ba.r[1].y, ba.r[2].y), V3(ba.r[0].z, ba.r[1].z, ba.r[2].z) };
+        V3 axisB(bb.r[0].x, bb.r[1].x, bb.r[2].x), axisB0(bb.r[0].y, bb.r[1].y, bb.r[2].y);
+        V3 delta = pivB - pivA;
+        V3 proj = pivA + dot(colA[0], delta) * colA[0];
+        V3 relPosA = proj - XA.o, relPosB = pivB - XB.o;
+        rel1 = relPosA - comA;
+        rel2 = relPosB - comB;
+        float depth[3];
+        for (int i = 0; i < 3; i++) {
+            nrm[i] = colA[i];
+            depth[i] = dot(delta, colA[i]);
+        }
+        bool solveLinLim = false;
+        if (sp[1] <= sp[0]) { // lower <= upper
+            if (depth[0] > sp[0]) {
+                depth[0] -= sp[0];
+                solveLinLim = true;
+            } else if (depth[0] < sp[1]) {
+                depth[0] -= sp[1];
+                solveLinLim = true;
+            } else {
+                depth[0] = 0.f;
+            }
+        } else {
+            depth[0] = 0.f;
+        }
+        float angDepth = 0.f;
+        bool solveAngLim = false;
+        if (sp[12] <= sp[11]) {
+            float rot = atan2fast(dot(axisB0, colA[2]), dot(axisB0, colA[1]));
+            if (rot < sp[12]) {
+                angDepth = rot - sp[12];
+                solveAngLim = true;
+            } else if (rot > sp[11]) {
+                angDepth = rot - sp[11];
+                solveAngLim = true;
+            }
+        }
+        M3 iwA(f4v(mwa.i0), f4v(mwa.i1), f4v(mwa.i2)), iwB(f4v(mwb.i0), f4v(mwb.i1), f4v(mwb.i2));
+        float kAngle = 1.0f / (dot(colA[0], xform_inv(iwA, colA[0])) + dot(colA[0], xform_inv(iwB, colA[0])));
+        const float *lin = solveLinLim ? sp + 2 : sp + 5, *ang = solveAngLim ? sp + 13 : sp + 16; // softness, restitution, damping
+        float d[3];
+        for (int i = 0; i < 3; i++) d[i] = jac_diag_inv(w2a, w2b, rel1, rel2, nrm[i], iiA, imA, iiB, imB);
+        s.n0 = v4(nrm[0], d[0]);
+        s.n1 = v4(nrm[1], d[1]);
+        s.n2 = v4(nrm[2], d[2]);
+        s.pa = v4(relPosA, __uint_as_float(flags));
+        s.pb = v4(relPosB, kAngle);
+        s.dpos = make_float4(depth[0], depth[1], depth[2], angDepth);
+        s.axis_a = v4(axisB, 0.f);
+        s.axis_b = make_float4(lin[0], lin[1], lin[2], sp[8]);   // axis row: softness, restitution, damping; orthogonal rows: softness
+        s.lim = make_float4(sp[9], sp[10], sp[21], sp[19]);      // orthogonal rows: restitution, damping; angular orthogonal: damping, softness
+        s.prm = make_float4(sp[20], ang[2], ang[1], ang[0]);     // angular orthogonal restitution; about the axis: damping, restitution, softness
+        a.out[j] = s;
+        return;
     } else {
         V3 relPos = pivB - pivA;
         if (is_zero_approx(length_squared(relPos))) nrm[0] = V3(1.0f, 0.f, 0.f);
@@ -791,6 +855,49 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
             if (dynA) A.ang += xform(A.iinv, impulse);
             if (dynB) B.ang += xform(B.iinv, -impulse);
         }
+    } else if (type == 3) { // slider (joints/bradot_slider_joint_3d.cpp:141-275; its motors cannot be switched on through the server)
+        V3 vel = (A.lin + cross(A.ang, pA - A.com)) - (B.lin + cross(B.ang, pB - B.com));
+        const float depth[3] = { js.dpos.x, js.dpos.y, js.dpos.z };
+        for (int i = 0; i < 3; i++) {
+            V3 normal = f4v(rows[i]);
+            float rel_vel = dot(normal, vel);
+            float softness = i ? js.axis_b.w : js.axis_b.x;
+            float restitution = i ? js.lim.x : js.axis_b.y;
+            float damping = i ? js.lim.y : js.axis_b.z;
+            float normalImpulse = softness * (restitution * depth[i] / a.dt - damping * rel_vel) * rows[i].w;
+            V3 iv = normal * normalImpulse;
+            if (dynA) apply_impulse(A, iv, pA);
+            if (dynB) apply_impulse(B, -iv, pB);
+        }
+        V3 axisA = f4v(js.n0), axisB = f4v(js.axis_a);
+        const V3 angVelA = A.ang, angVelB = B.ang; // by value, as get_angular_velocity() returns them
+        V3 aroundA = axisA * dot(axisA, angVelA);
+        V3 aroundB = axisB * dot(axisB, angVelB);
+        V3 angAorthog = angVelA - aroundA;
+        V3 angBorthog = angVelB - aroundB;
+        V3 velrelOrthog = angAorthog - angBorthog;
+        const float dampOrthoAng = js.lim.z, softOrthoAng = js.lim.w, restOrthoAng = js.prm.x;
+        float len = length(velrelOrthog);
+        if (len > 0.00001f) {
+            V3 normal = normalized(velrelOrthog);
+            float denom = ang_denominator(A, normal) + ang_denominator(B, normal);
+            velrelOrthog *= (1.0f / denom) * dampOrthoAng * softOrthoAng;
+        }
+        V3 angularError = cross(axisA, axisB) * (1.0f / a.dt);
+        float len2 = length(angularError);
+        if (len2 > 0.00001f) {
+            V3 normal2 = normalized(angularError);
+            float denom2 = ang_denominator(A, normal2) + ang_denominator(B, normal2);
+            angularError *= (1.0f / denom2) * restOrthoAng * softOrthoAng;
+        }
+        if (dynA) A.ang += xform(A.iinv, -velrelOrthog + angularError);
+        if (dynB) B.ang += xform(B.iinv, velrelOrthog - angularError);
+        // about the axis: limit or free motion, the parameters were chosen by the setup
+        float impulseMag = dot(angVelB - angVelA, axisA) * js.prm.y + js.dpos.w * js.prm.z / a.dt;
+        impulseMag *= js.pb.w * js.prm.w;
+        V3 impulse = axisA * impulseMag;
+        if (dynA) A.ang += xform(A.iinv, impulse);
+        if (dynB) B.ang += xform(B.iinv, -impulse);
     } else { // hinge: one velocity sample for the three linear rows
         V3 vel1 = A.lin + cross(A.ang, pA - A.com);
         V3 vel2 = B.lin + cross(B.ang, pB - B.com);
@@ -1082,6 +1189,7 @@ int bpc_launch_joint_setup(bpc_context *ctx, float dt) {
     JsArgs a;
     a.n = nj;
     a.joints = ctx->d_joints.p;
+    a.jext = ctx->h_jext.empty() ? nullptr : ctx->d_jext.p;
     a.out = ctx->jsetup.p;
     a.xf = ctx->xf.p;
     a.massw = ctx->massw.p;

@@ -16,7 +16,7 @@ import numpy as np
 
 SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONVEX, SHAPE_CONCAVE, SHAPE_HEIGHTMAP = range(9)
 MODE_STATIC, MODE_KINEMATIC, MODE_RIGID, MODE_RIGID_LINEAR = range(4)
-JOINT_PIN, JOINT_HINGE, JOINT_CONE_TWIST = 0, 1, 2
+JOINT_PIN, JOINT_HINGE, JOINT_CONE_TWIST, JOINT_SLIDER = 0, 1, 2, 3
 
 SHAPE_DT = np.dtype([("type", "<u4"), ("p", "<f4", 4), ("vert_ofs", "<u4"), ("vert_cnt", "<u4"), ("pad", "<u4")])
 BODY_DT = np.dtype([
@@ -29,6 +29,9 @@ BODY_DT = np.dtype([
 # lower, limit bias, limit softness, limit relaxation, motor target velocity, motor max impulse); priority 0 = default (1)
 JOINT_DT = np.dtype([("type", "<u4"), ("body_a", "<u4"), ("body_b", "<u4"), ("flags", "<u4"),
                      ("fa", "<f4", 12), ("fb", "<f4", 12), ("params", "<f4", 8), ("priority", "<u4"), ("pad", "<u4", 3)])
+# long parameter table of a joint (bpc_joint_params_write): `count` values from parameter `first` on; a slider joint's 22
+# values are in PhysicsServer3D::SliderJointParam order
+JOINT_EXT_DT = np.dtype([("joint", "<u4"), ("first", "<u4"), ("count", "<u4"), ("pad", "<u4"), ("values", "<f4", 28)])
 # bpc_area_desc as is.  flags: bit0 monitorable, bit1 body monitor callback (events), bit2 gravity is a point; override modes:
 # PhysicsServer3D::AreaSpaceOverrideMode (0 disabled, 1 combine, 2 combine-replace, 3 replace, 4 replace-combine)
 AREA_DT = np.dtype([("space", "<i4"), ("shape", "<i4"), ("flags", "<u4"), ("priority", "<i4"), ("xf", "<f4", 12), ("shape_xf", "<f4", 12),
@@ -59,6 +62,7 @@ class Scene:
         self.bodies = np.zeros(0, BODY_DT)
         self.joints = np.zeros(0, JOINT_DT)
         self.areas = np.zeros(0, AREA_DT)
+        self.joint_ext = np.zeros(0, JOINT_EXT_DT)
         self.verts = np.zeros((0, 3), np.float32)
 
     # -- builders -------------------------------------------------------------
@@ -103,6 +107,13 @@ class Scene:
         self.joints = np.concatenate([self.joints, rec])
         return first
 
+    def set_joint_params(self, joint, first, values):
+        """Values of a joint's long parameter table (slider), from parameter `first` on."""
+        rec = np.zeros(1, JOINT_EXT_DT)
+        rec["joint"], rec["first"], rec["count"] = joint, first, len(values)
+        rec["values"][0, :len(values)] = values
+        self.joint_ext = np.concatenate([self.joint_ext, rec])
+
     def add_areas(self, n, **fields):
         rec = np.zeros(n, AREA_DT)
         rec["xf"] = IDENT12
@@ -126,7 +137,7 @@ class Scene:
     # -- file I/O ---------------------------------------------------------------
     def write(self, path):
         hdr = struct.pack("<4sIIIIIIfI7I", b"BSCN", 2, self.n_spaces, len(self.shapes), len(self.bodies),
-                          len(self.joints), len(self.verts), float(self.dt), self.iterations, self.iter_step, len(self.areas), *([0] * 5))
+                          len(self.joints), len(self.verts), float(self.dt), self.iterations, self.iter_step, len(self.areas), len(self.joint_ext), *([0] * 4))
         with open(path, "wb") as f:
             f.write(hdr)
             f.write(self.shapes.tobytes())
@@ -134,12 +145,13 @@ class Scene:
             f.write(self.joints.tobytes())
             f.write(np.ascontiguousarray(self.verts, np.float32).tobytes())
             f.write(self.areas.tobytes())
+            f.write(self.joint_ext.tobytes())
 
     @staticmethod
     def read(path):
         with open(path, "rb") as f:
             raw = f.read()
-        magic, ver, nsp, nsh, nb, nj, nv, dt, it, its, na = struct.unpack_from("<4sIIIIIIfIII", raw, 0)
+        magic, ver, nsp, nsh, nb, nj, nv, dt, it, its, na, nje = struct.unpack_from("<4sIIIIIIfIIII", raw, 0)
         assert magic == b"BSCN" and ver == 2
         off = struct.calcsize("<4sIIIIIIfI7I")
         sc = Scene(nsp, dt, it)
@@ -153,6 +165,8 @@ class Scene:
         sc.verts = np.frombuffer(raw, "<f4", nv * 3, off).reshape(-1, 3).copy()
         off += nv * 12
         sc.areas = np.frombuffer(raw, AREA_DT, na, off).copy()
+        off += na * AREA_DT.itemsize
+        sc.joint_ext = np.frombuffer(raw, JOINT_EXT_DT, nje, off).copy()
         return sc
 
 
@@ -563,6 +577,50 @@ def hanging_chains(n_chains=12, chain_len=5, seed=5, cone_twist=False):
                     prm[0], prm[1], prm[2] = 0.5, 0.8, 0.05
                 sc.add_joints(1, type=JOINT_PIN, body_a=first + k, body_b=first + k + 1, flags=flags, fa=fa, fb=fb, params=prm, priority=prio)
                 pin_i += 1
+    return sc
+
+
+def slider_rigs(n_rigs=18, seed=11):
+    """Slider joints: rig r is a static anchor, a box hanging from it by a slider joint and a second box on the first by
+    another one; no collisions (joint-only islands, as in hanging_chains).  The joint frames are turned so that the slider
+    axis is no body axis; rig r % 3 == 0 keeps every default (no linear limit: lower > upper; angular limit [0, 0], always
+    engaged), the others get linear limits narrow enough to be hit, an angular range, and their own softness / restitution /
+    damping values for every branch; rigs with r % 4 == 3 run at solver priority 2."""
+    sc = Scene(name="slider_rigs_%d" % n_rigs)
+    anchor = sc.add_shape(SHAPE_BOX, (0.1, 0.1, 0.1))
+    link = sc.add_shape(SHAPE_BOX, (0.3, 0.12, 0.2))
+    rng = np.random.default_rng(seed)
+    for r in range(n_rigs):
+        x0 = r * 8.0
+        xa = IDENT12.copy()
+        xa[9], xa[10] = x0, 10.0
+        a = sc.add_bodies(1, mode=MODE_STATIC, shape=anchor, xf=xa, layer=0, mask=0)
+        xf = np.tile(IDENT12, (2, 1))
+        xf[:, 9] = x0 + np.array([0.5, 1.3])
+        xf[:, 10] = 10.0 - np.array([0.3, 0.7])
+        lin = rng.uniform(-1.5, 1.5, (2, 3)).astype(np.float32)
+        ang = rng.uniform(-1.5, 1.5, (2, 3)).astype(np.float32)
+        first = sc.add_bodies(2, shape=link, xf=xf, mass=0.6 + 0.3 * (r % 3), layer=0, mask=0, linvel=lin, angvel=ang, flags=0)
+        prio = 2 if r % 4 == 3 else 0
+        for k, (ba, bb) in enumerate(((a, first), (first, first + 1))):
+            th, ph = 0.25 * ((r + k) % 4), 0.3 * ((r + 2 * k) % 3)
+            c, s, c2, s2 = np.cos(th), np.sin(th), np.cos(ph), np.sin(ph)
+            rz = np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]])
+            rx = np.array([[1, 0, 0], [0, c2, -s2], [0, s2, c2]])
+            fa, fb = IDENT12.copy(), IDENT12.copy()
+            fa[0:9] = (rz @ rx).reshape(-1)
+            fb[0:9] = (rz @ rx @ np.array([[1, 0, 0], [0, np.cos(0.15 * k), -np.sin(0.15 * k)], [0, np.sin(0.15 * k), np.cos(0.15 * k)]])).reshape(-1)
+            fa[9:12] = (0.4, -0.2, 0.0)
+            fb[9:12] = (-0.35, 0.1, 0.05)
+            j = sc.add_joints(1, type=JOINT_SLIDER, body_a=ba, body_b=bb, flags=JOINT_NO_COLLIDE, fa=fa, fb=fb, priority=prio)
+            if r % 3 != 0:
+                v = np.array([0.08 + 0.05 * k, -0.12, 0.9, 0.6, 0.8, 0.95, 0.65, 0.1 * (r % 2), 0.9, 0.75, 0.85,
+                              0.3, -0.2 - 0.1 * k, 0.85, 0.6, 0.9, 0.9, 0.5, 0.2 * (r % 2), 0.95, 0.65, 0.8], np.float32)
+                if r % 3 == 2:
+                    sc.set_joint_params(j, 0, v)
+                else:           # only some of them: the linear limits and the angular block
+                    sc.set_joint_params(j, 0, v[0:2])
+                    sc.set_joint_params(j, 11, v[11:22])
     return sc
 
 

@@ -42,7 +42,7 @@ EXPORTS = [
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
     "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
     "bpc_bodies_set_state", "bpc_bodies_read_slots", "bpc_bodies_write_slots", "bpc_bodies_read_state", "bpc_reserve",
-    "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_test_segment_math", "bpc_bodies_set_exception",
+    "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_joint_params_write", "bpc_joint_params_read", "bpc_test_segment_math", "bpc_bodies_set_exception",
     "bpc_bodies_set_max_contacts_reported", "bpc_body_read_contacts", "bpc_contacts_capacity", "bpc_contacts_read",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
     "bpc_space_set_query_exclude", "bpc_space_rest_infos", "bpc_space_cast_motions",
@@ -98,6 +98,8 @@ def load_library(path=LIB_PATH):
     lib.bpc_joints_create.argtypes = [vp, vp, ci]
     lib.bpc_joints_write.argtypes = [vp, ci, ci, vp]
     lib.bpc_joints_destroy.argtypes = [vp, ci, ci]
+    lib.bpc_joint_params_write.argtypes = [vp, ci, ci, ci, vp]
+    lib.bpc_joint_params_read.argtypes = [vp, ci, ci, ci, vp]
     lib.bpc_joint_count.argtypes = [vp]
     lib.bpc_space_set_active.argtypes = [vp, ci, ci]
     lib.bpc_space_destroy.argtypes = [vp, ci]
@@ -341,6 +343,16 @@ class PhysicsServerCUDA:
         rec = np.ascontiguousarray(records, scenes.JOINT_DT)
         self._check(self.lib.bpc_joints_write(self.ctx, int(first), len(rec), _ptr(rec)))
 
+    def joint_params_write(self, joint, first, values):
+        """slider_joint_set_param: values of the joint's long parameter table from parameter `first` on."""
+        v = np.ascontiguousarray(values, np.float32).reshape(-1)
+        self._check(self.lib.bpc_joint_params_write(self.ctx, int(joint), int(first), len(v), _ptr(v)))
+
+    def joint_params_read(self, joint, first=0, n=22):
+        v = np.zeros(n, np.float32)
+        self._check(self.lib.bpc_joint_params_read(self.ctx, int(joint), int(first), int(n), _ptr(v)))
+        return v
+
     def joints_destroy(self, first, n=1):
         self._check(self.lib.bpc_joints_destroy(self.ctx, int(first), int(n)))
 
@@ -533,6 +545,8 @@ class PhysicsServerCUDA:
             self.bodies_set_max_contacts_reported(first + idx, want[idx])
         if len(sc.joints):
             self.joints_create(sc.joints)
+            for e in sc.joint_ext:
+                self.joint_params_write(int(e["joint"]), int(e["first"]), e["values"][:int(e["count"])])
         if len(getattr(sc, "areas", ())):
             self.areas_create(sc.areas)
         return first

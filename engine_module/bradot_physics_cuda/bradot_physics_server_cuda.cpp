@@ -1418,7 +1418,7 @@ void BradotPhysicsServerCUDA::_fill_joint_desc(const Joint *p_joint, bpc_joint_d
 	const Joint *j = p_joint;
 	const Body *a = body_owner.get_or_null(j->a), *b = body_owner.get_or_null(j->b);
 	r_desc = {};
-	r_desc.type = j->type == JOINT_TYPE_PIN ? BPC_JOINT_PIN : (j->type == JOINT_TYPE_HINGE ? BPC_JOINT_HINGE : BPC_JOINT_CONE_TWIST);
+	r_desc.type = j->type == JOINT_TYPE_PIN ? BPC_JOINT_PIN : (j->type == JOINT_TYPE_HINGE ? BPC_JOINT_HINGE : (j->type == JOINT_TYPE_SLIDER ? BPC_JOINT_SLIDER : BPC_JOINT_CONE_TWIST));
 	r_desc.body_a = a ? a->slot : 0;
 	r_desc.body_b = b ? b->slot : 0;
 	r_desc.flags = (j->disable_collisions ? 1 : 0) | 8; // parameters are always given
@@ -1428,6 +1428,8 @@ void BradotPhysicsServerCUDA::_fill_joint_desc(const Joint *p_joint, bpc_joint_d
 		for (int k = 0; k < 3; k++) {
 			r_desc.params[k] = j->pin_params[k];
 		}
+	} else if (j->type == JOINT_TYPE_SLIDER) {
+		// its values go through bpc_joint_params_write
 	} else if (j->type == JOINT_TYPE_CONE_TWIST) {
 		for (int k = 0; k < CONE_TWIST_MAX + 1; k++) {
 			r_desc.params[k] = j->cone_params[k];
@@ -1603,6 +1605,42 @@ bool BradotPhysicsServerCUDA::hinge_joint_get_flag(RID p_joint, HingeJointFlag p
 	ERR_FAIL_COND_V(joint->type != JOINT_TYPE_HINGE, false);
 	ERR_FAIL_INDEX_V((int)p_flag, (int)HINGE_JOINT_FLAG_MAX, false);
 	return joint->hinge_flags[p_flag];
+}
+
+// joint_make_slider / slider_joint_*_param (bradot_physics_server_3d.cpp:1421-1459; the joint itself:
+// joints/bradot_slider_joint_3d.cpp)
+void BradotPhysicsServerCUDA::joint_make_slider(RID p_joint, RID p_body_A, const Transform3D &p_local_frame_A, RID p_body_B, const Transform3D &p_local_frame_B) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body_A));
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body_B));
+	joint_clear(p_joint);
+	joint->type = JOINT_TYPE_SLIDER;
+	joint->a = p_body_A;
+	joint->b = p_body_B;
+	joint->fa = p_local_frame_A;
+	joint->fb = p_local_frame_B;
+	joint->pending = true;
+	pending_joints.push_back(joint);
+}
+
+void BradotPhysicsServerCUDA::slider_joint_set_param(RID p_joint, SliderJointParam p_param, real_t p_value) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND(joint->type != JOINT_TYPE_SLIDER);
+	ERR_FAIL_INDEX((int)p_param, (int)SLIDER_JOINT_MAX);
+	joint->slider_params[p_param] = p_value;
+	if (joint->handle >= 0) {
+		ERR_FAIL_COND_MSG(bpc_joint_params_write(ctx, joint->handle, (int)p_param, 1, &joint->slider_params[p_param]) < 0, bpc_last_error(ctx));
+	}
+}
+
+real_t BradotPhysicsServerCUDA::slider_joint_get_param(RID p_joint, SliderJointParam p_param) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, 0);
+	ERR_FAIL_COND_V(joint->type != JOINT_TYPE_SLIDER, 0);
+	ERR_FAIL_INDEX_V((int)p_param, (int)SLIDER_JOINT_MAX, 0);
+	return joint->slider_params[p_param];
 }
 
 // joint_make_cone_twist / cone_twist_joint_*_param (bradot_physics_server_3d.cpp:1461-1499; the joint itself:
@@ -2249,6 +2287,9 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 			for (uint32_t i = 0; i < uploaded.size(); i++) {
 				uploaded[i]->handle = first + i;
 				uploaded[i]->pending = false;
+				if (uploaded[i]->type == JOINT_TYPE_SLIDER) {
+					ERR_FAIL_COND_MSG(bpc_joint_params_write(ctx, first + i, 0, SLIDER_JOINT_MAX, uploaded[i]->slider_params) < 0, bpc_last_error(ctx));
+				}
 			}
 		}
 	}

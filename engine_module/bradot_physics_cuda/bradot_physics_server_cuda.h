@@ -6,7 +6,7 @@
 // Implemented by hand: what a scene of RigidBody3D / StaticBody3D nodes needs -- spaces (create, activate, parameters, free),
 // world-boundary / sphere / box / capsule / convex shapes, bodies with one shape (every setter also after the body is in a
 // space; state-sync and force-integration callbacks; PhysicsDirectBodyState3D; impulses, forces, constant forces; axis
-// locks; collision exceptions; free), pin, hinge and cone-twist joints with their parameters, flags and solver priority, step, stats,
+// locks; collision exceptions; free), pin, hinge, slider and cone-twist joints with their parameters, flags and solver priority, step, stats,
 // PhysicsDirectSpaceState3D queries.  Every other pure virtual of the interface gets a generated default override
 // (engine_module/gen_stubs.py) that logs once and returns the type's default, which is how the reference answers an
 // invalid RID.
@@ -162,6 +162,9 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		// ConeTwistJointParam order, then the second swing span (bradot_cone_twist_joint_3d.h:80-86: tau / 8 and 0 until
 		// SWING_SPAN is set, which writes both)
 		real_t cone_params[CONE_TWIST_MAX + 1] = { Math_TAU / 8.0, 0.0, 0.3, 0.0, 1.0, 0.0 };
+		// SliderJointParam order; the members of BradotSliderJoint3D as constructed (joints/bradot_slider_joint_3d.h:80-110)
+		float slider_params[SLIDER_JOINT_MAX] = { -1.0f, 1.0f, 1.0f, 0.7f, 1.0f, 1.0f, 0.7f, 0.0f, 1.0f, 0.7f, 1.0f,
+			0.0f, 0.0f, 1.0f, 0.7f, 1.0f, 1.0f, 0.7f, 0.0f, 1.0f, 0.7f, 1.0f };
 		bool pending = false;
 		int handle = -1;
 	};
@@ -372,6 +375,9 @@ public:
 	virtual real_t hinge_joint_get_param(RID p_joint, HingeJointParam p_param) const override;
 	virtual void hinge_joint_set_flag(RID p_joint, HingeJointFlag p_flag, bool p_enabled) override;
 	virtual bool hinge_joint_get_flag(RID p_joint, HingeJointFlag p_flag) const override;
+	virtual void joint_make_slider(RID p_joint, RID p_body_A, const Transform3D &p_local_frame_A, RID p_body_B, const Transform3D &p_local_frame_B) override;
+	virtual void slider_joint_set_param(RID p_joint, SliderJointParam p_param, real_t p_value) override;
+	virtual real_t slider_joint_get_param(RID p_joint, SliderJointParam p_param) const override;
 	virtual void joint_make_cone_twist(RID p_joint, RID p_body_A, const Transform3D &p_local_frame_A, RID p_body_B, const Transform3D &p_local_frame_B) override;
 	virtual void cone_twist_joint_set_param(RID p_joint, ConeTwistJointParam p_param, real_t p_value) override;
 	virtual real_t cone_twist_joint_get_param(RID p_joint, ConeTwistJointParam p_param) const override;

@@ -34,7 +34,8 @@ public:
 };
 
 #pragma pack(push, 1)
-struct ScnHeader { char magic[4]; uint32_t version, n_spaces, n_shapes, n_bodies, n_joints, n_verts; float dt; uint32_t iterations, iter_step, n_areas, reserved[5]; };
+struct ScnHeader { char magic[4]; uint32_t version, n_spaces, n_shapes, n_bodies, n_joints, n_verts; float dt; uint32_t iterations, iter_step, n_areas, n_joint_ext, reserved[4]; };
+struct ScnJointExt { uint32_t joint, first, count, pad; float values[28]; };
 struct ScnShape { uint32_t type; float p[4]; uint32_t vert_ofs, vert_cnt, pad; };
 struct ScnBody { uint32_t space, mode, shape, flags; float xf[12], shape_xf[12], linvel[3], angvel[3], mass, friction, bounce, gravity_scale, lin_damp, ang_damp; uint32_t layer, mask; };
 struct ScnJoint { uint32_t type, body_a, body_b, flags; float fa[12], fb[12], params[8]; uint32_t priority, pad[3]; };
@@ -138,6 +139,8 @@ int main(int argc, char **argv) {
 	if (hd.n_verts && fread(verts.data(), 12, hd.n_verts, sf) != hd.n_verts) return 2;
 	std::vector<ScnArea> sareas(hd.n_areas);
 	if (hd.n_areas && fread(sareas.data(), sizeof(ScnArea), hd.n_areas, sf) != hd.n_areas) return 2;
+	std::vector<ScnJointExt> sjext(hd.n_joint_ext);
+	if (hd.n_joint_ext && fread(sjext.data(), sizeof(ScnJointExt), hd.n_joint_ext, sf) != hd.n_joint_ext) return 2;
 	fclose(sf);
 
 	OSHeadless os;
@@ -276,6 +279,13 @@ int main(int argc, char **argv) {
 			if (j.flags & 8) {
 				for (int k = 0; k < 3; k++) {
 					ps->pin_joint_set_param(jr, (PhysicsServer3D::PinJointParam)k, j.params[k]);
+				}
+			}
+		} else if (j.type == 3) {
+			ps->joint_make_slider(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
+			for (const ScnJointExt &e : sjext) {
+				for (uint32_t k = 0; e.joint == (uint32_t)joint_r.size() && k < e.count; k++) {
+					ps->slider_joint_set_param(jr, (PhysicsServer3D::SliderJointParam)(e.first + k), e.values[k]);
 				}
 			}
 		} else if (j.type == 2) {

@@ -21,7 +21,8 @@ typedef struct bpc_context bpc_context;
 
 enum { BPC_SHAPE_WORLD_BOUNDARY = 0, BPC_SHAPE_SPHERE = 2, BPC_SHAPE_BOX = 3, BPC_SHAPE_CAPSULE = 4, BPC_SHAPE_CONVEX_POLYGON = 6 };
 enum { BPC_BODY_MODE_STATIC = 0, BPC_BODY_MODE_KINEMATIC = 1, BPC_BODY_MODE_RIGID = 2, BPC_BODY_MODE_RIGID_LINEAR = 3 };
-enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1, BPC_JOINT_CONE_TWIST = 2 };
+enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1, BPC_JOINT_CONE_TWIST = 2, BPC_JOINT_SLIDER = 3 };
+#define BPC_SLIDER_PARAMS 22 /* PhysicsServer3D::SLIDER_JOINT_MAX */
 
 /* Bulk body description; one record per body.  Same layout as the record of the neutral scene
  * file (bradot_b200/scenes.py BODY_DT).  Replaces the per-body call sequence body_create /
@@ -255,6 +256,13 @@ int bpc_joints_write(bpc_context *ctx, int first, int n, const bpc_joint_desc *d
 /* joint_clear / free(joint) (P3D/bradot_physics_server_3d.cpp:1229-1246, 1592-1601): the joint stops acting, the collision
  * exception it made is dropped; indices of other joints do not move. */
 int bpc_joints_destroy(bpc_context *ctx, int first, int n);
+/* The long parameter table of a joint whose parameters do not fit `bpc_joint_desc.params`: a slider joint's 22 values in
+ * PhysicsServer3D::SliderJointParam order (slider_joint_set_param / slider_joint_get_param,
+ * P3D/joints/bradot_slider_joint_3d.cpp:349-479; defaults P3D/joints/bradot_slider_joint_3d.h:80-110, which a new slider
+ * joint starts with -- its `params` and the `params holds values` flag are ignored).  Write / read `n` values starting at
+ * parameter `first`.  Slider frames: the joint slides along the x axis of frame A. */
+int bpc_joint_params_write(bpc_context *ctx, int joint, int first, int n, const float *values);
+int bpc_joint_params_read(bpc_context *ctx, int joint, int first, int n, float *values);
 int bpc_joint_count(bpc_context *ctx);
 
 /* ---- the step: BradotPhysicsServer3D::step -> BradotStep3D::step for every space at once

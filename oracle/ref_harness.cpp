@@ -74,7 +74,12 @@ struct ScnHeader {
 	uint32_t iterations;
 	uint32_t iter_step; // space s sweeps iterations + s * iter_step times
 	uint32_t n_areas; // area records after the vertices
-	uint32_t reserved[5];
+	uint32_t n_joint_ext; // long joint parameter rows after the areas
+	uint32_t reserved[4];
+};
+struct ScnJointExt { // `count` values of joint `joint` from parameter `first` on (slider: SliderJointParam order)
+	uint32_t joint, first, count, pad;
+	float values[28];
 };
 struct ScnShape {
 	uint32_t type; // PhysicsServer3D::ShapeType
@@ -873,6 +878,8 @@ int main(int argc, char **argv) {
 	if (hd.n_verts && fread(sverts.data(), 12, hd.n_verts, sf) != hd.n_verts) return 2;
 	std::vector<ScnArea> sareas(hd.n_areas);
 	if (hd.n_areas && fread(sareas.data(), sizeof(ScnArea), hd.n_areas, sf) != hd.n_areas) return 2;
+	std::vector<ScnJointExt> sjext(hd.n_joint_ext);
+	if (hd.n_joint_ext && fread(sjext.data(), sizeof(ScnJointExt), hd.n_joint_ext, sf) != hd.n_joint_ext) return 2;
 	fclose(sf);
 
 	// ---- minimal engine bring-up (order follows Main::test_setup, main/main.cpp:705-747)
@@ -1027,13 +1034,21 @@ int main(int argc, char **argv) {
 			ps->joint_make_pin(jr, w.bodies[j.body_a], Vector3(j.fa[9], j.fa[10], j.fa[11]), w.bodies[j.body_b], Vector3(j.fb[9], j.fb[10], j.fb[11]));
 		} else if (j.type == 2) {
 			ps->joint_make_cone_twist(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
+		} else if (j.type == 3) {
+			ps->joint_make_slider(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		} else {
 			ps->joint_make_hinge(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		}
 		if (j.flags & 1) {
 			ps->joint_disable_collisions_between_bodies(jr, true);
 		}
-		if (j.flags & 8) {
+		if (j.type == 3) {
+			for (const ScnJointExt &e : sjext) {
+				for (uint32_t k = 0; e.joint == i && k < e.count; k++) {
+					ps->slider_joint_set_param(jr, (PhysicsServer3D::SliderJointParam)(e.first + k), e.values[k]);
+				}
+			}
+		} else if (j.flags & 8) {
 			if (j.type == 0) {
 				for (int k = 0; k < 3; k++) {
 					ps->pin_joint_set_param(jr, (PhysicsServer3D::PinJointParam)k, j.params[k]);

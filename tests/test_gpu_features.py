@@ -423,6 +423,33 @@ def test_height_maps_match_the_reference():
     assert w["contact"] < CONTACT_TOL and w["state"] < 1e-4, w
 
 
+def test_slider_joints_match_the_reference():
+    """SliderJoint3D (joints/bradot_slider_joint_3d.cpp:74-337): rigs of two boxes on slider joints in turned frames, default and
+    own parameters (22 per joint through bpc_joint_params_write), linear and angular limits hit; teacher-forced with the
+    reference's sweep order, body state after the step within 1e-4.  The parameters are at work: the same rigs with every
+    default swing differently; and a parameter written at run time reads back."""
+    _need_oracle()
+    sc = scenes.slider_rigs()
+    assert (sc.joints["type"] == scenes.JOINT_SLIDER).sum() == 36 and len(sc.joint_ext) >= 24
+    _, dump = parity.run_oracle(sc, 80)
+    w = parity.teacher_forced(sc, 80, [1, 2, 5, 15, 30, 50, 79], dump=dump)
+    assert w["state"] < STATE_TOL, w
+    plain = scenes.slider_rigs()
+    plain.joint_ext = plain.joint_ext[:0]
+    ps = parity.new_server(plain, dump)
+    parity.load_state(ps, dump, 30)
+    ps.set_solve_order(parity.solve_order(dump, 31))
+    ps.step(sc.dt)
+    av = ps.bodies_read(server.FIELD_ANGULAR_VELOCITY)
+    assert parity.rel_err(av, dump[("bodies", 31)][:, 15:18], 1.0) > 1e-2
+    assert np.allclose(ps.joint_params_read(0), [-1, 1, 1, .7, 1, 1, .7, 0, 1, .7, 1, 0, 0, 1, .7, 1, 1, .7, 0, 1, .7, 1])
+    ps.joint_params_write(0, 3, [0.25, 0.5])
+    assert np.array_equal(ps.joint_params_read(0, 2, 4), np.array([1, 0.25, 0.5, 1], np.float32))
+    with pytest.raises(Exception):
+        ps.joint_params_write(0, 20, [1, 2, 3])
+    ps.finish()
+
+
 def test_cone_twist_joints_match_the_reference():
     """ConeTwistJoint3D (joints/bradot_cone_twist_joint_3d.cpp:67-279: swing ellipse and twist limits with accumulated, clamped
     impulses, the shortest-arc quaternion for the twist reference): chains whose links alternate hinges and cone-twist joints,
