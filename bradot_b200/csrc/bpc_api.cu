@@ -44,7 +44,7 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     ctx->xf.free_(); ctx->shape_xf.free_(); ctx->vel.free_(); ctx->massw.free_(); ctx->props.free_(); ctx->forces.free_();
-    ctx->meta.free_(); ctx->io_slots.free_(); ctx->shape_id.free_(); ctx->shape_p.free_(); ctx->np_work.free_(); ctx->np_cwork.free_(); ctx->staging.free_(); ctx->a_range.free_(); ctx->a_range_cur.free_(); ctx->jsetup.free_(); ctx->items.free_(); ctx->npairs.free_(); ctx->tree_items.free_(); ctx->kin.free_(); ctx->kin_ids.free_(); ctx->ccd_ids.free_();
+    ctx->meta.free_(); ctx->io_slots.free_(); ctx->shape_id.free_(); ctx->shape_p.free_(); ctx->np_work.free_(); ctx->np_cwork.free_(); ctx->staging.free_(); ctx->a_range.free_(); ctx->a_range_cur.free_(); ctx->jsetup.free_(); ctx->jsetup6.free_(); ctx->items.free_(); ctx->npairs.free_(); ctx->tree_items.free_(); ctx->kin.free_(); ctx->kin_ids.free_(); ctx->ccd_ids.free_();
     ctx->island.free_(); ctx->island_flag.free_(); ctx->shapes.free_(); ctx->meshes.free_(); ctx->mverts.free_();
     ctx->mplanes.free_(); ctx->medges.free_(); ctx->mfaces.free_(); ctx->mindex.free_(); ctx->d_spaces.free_();
     ctx->d_areas.free_(); ctx->area_list.free_(); ctx->area_start.free_(); ctx->body_area_cnt.free_(); ctx->body_area.free_(); ctx->area_events.free_();

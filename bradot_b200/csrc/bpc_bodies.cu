@@ -543,7 +543,7 @@ static void joint_defaults(JointRec &j) {
         j.prm[4] = 1.0f;
         return;
     }
-    if (j.type == BPC_JOINT_SLIDER) { // its values are in the long table
+    if (j.type == BPC_JOINT_SLIDER || j.type == BPC_JOINT_6DOF) { // its values are in the long table
         memset(j.prm, 0, sizeof(j.prm));
         return;
     }
@@ -565,6 +565,18 @@ static void slider_defaults(float *p) {
     memcpy(p, v, sizeof(v));
 }
 
+// BradotG6DOFTranslationalLimitMotor3D / BradotG6DOFRotationalLimitMotor3D as constructed (bradot_generic_6dof_joint_3d.h:67-112)
+static void g6dof_defaults(float *p) {
+    for (int ax = 0; ax < 3; ax++) {
+        float *q = p + ax * BPC_G6DOF_AXIS_STRIDE;
+        memset(q, 0, BPC_G6DOF_AXIS_STRIDE * sizeof(float));
+        q[2] = 0.7f; q[3] = 0.5f; q[4] = 1.0f;                  // linear softness, restitution, damping (limits 0 / 0)
+        q[10] = -1e30f; q[11] = 1e30f; q[12] = 0.5f; q[13] = 1.0f; // angular lo, hi, softness, damping
+        q[15] = 300.0f; q[16] = 0.5f; q[18] = 0.1f;             // max limit force, ERP, max motor force
+        q[22] = 1.0f;                                           // linear limit enabled
+    }
+}
+
 // collision exceptions are those of the live joints that ask for them
 static void rebuild_exceptions(bpc_context *ctx) {
     ctx->h_except = ctx->h_except_user;
@@ -581,7 +593,7 @@ static int joint_from_desc(bpc_context *ctx, const bpc_joint_desc &d, JointRec &
     static_assert(sizeof(JointRec) == sizeof(bpc_joint_desc), "JointRec mirrors bpc_joint_desc");
     if (d.body_a >= ctx->n_bodies || d.body_b >= ctx->n_bodies || d.body_a == d.body_b || ctx->h_dead[d.body_a] || ctx->h_dead[d.body_b])
         return fail(ctx, "joint: invalid body");
-    if (d.type > BPC_JOINT_SLIDER) return fail(ctx, "joint: unsupported joint type (pin, hinge, cone twist)");
+    if (d.type > BPC_JOINT_6DOF) return fail(ctx, "joint: unsupported joint type (pin, hinge, cone twist)");
     if (d.priority > 15) return fail(ctx, "joint: solver priority above 15");
     memcpy(&j, &d, sizeof(JointRec));
     j.flags &= ~JF_DEAD;
@@ -600,11 +612,15 @@ extern "C" int bpc_joints_create(bpc_context *ctx, const bpc_joint_desc *descs, 
     }
     ctx->h_joints.insert(ctx->h_joints.end(), recs.begin(), recs.end());
     bool want_ext = !ctx->h_jext.empty();
-    for (const JointRec &r : recs) want_ext |= r.type == BPC_JOINT_SLIDER;
+    for (const JointRec &r : recs) {
+        want_ext |= r.type == BPC_JOINT_SLIDER || r.type == BPC_JOINT_6DOF;
+        ctx->have_g6dof |= r.type == BPC_JOINT_6DOF;
+    }
     if (want_ext) {
         ctx->h_jext.resize(ctx->h_joints.size() * JEXT_STRIDE, 0.f);
         for (int i = 0; i < n; i++)
             if (recs[i].type == BPC_JOINT_SLIDER) slider_defaults(&ctx->h_jext[(size_t)(first + i) * JEXT_STRIDE]);
+            else if (recs[i].type == BPC_JOINT_6DOF) g6dof_defaults(&ctx->h_jext[(size_t)(first + i) * JEXT_STRIDE]);
     }
     rebuild_exceptions(ctx);
     ctx->joints_dirty = true;
@@ -667,8 +683,9 @@ extern "C" int bpc_bodies_set_exception(bpc_context *ctx, int body_a, int body_b
 static int jext_check(bpc_context *ctx, const char *who, int joint, int first, int n, const void *values) {
     const char *why = nullptr;
     if (joint < 0 || (size_t)joint >= ctx->h_joints.size() || (ctx->h_joints[joint].flags & JF_DEAD)) why = ": invalid joint";
-    else if (ctx->h_joints[joint].type != BPC_JOINT_SLIDER) why = ": this joint type has no long parameter table";
-    else if (first < 0 || n < 0 || first + n > BPC_SLIDER_PARAMS || (n > 0 && !values)) why = ": parameter range out of bounds";
+    else if (ctx->h_joints[joint].type != BPC_JOINT_SLIDER && ctx->h_joints[joint].type != BPC_JOINT_6DOF) why = ": this joint type has no long parameter table";
+    else if (first < 0 || n < 0 || first + n > (ctx->h_joints[joint].type == BPC_JOINT_SLIDER ? BPC_SLIDER_PARAMS : BPC_G6DOF_PARAMS) || (n > 0 && !values))
+        why = ": parameter range out of bounds";
     if (!why) return 0;
     return fail(ctx, (std::string(who) + why).c_str());
 }

@@ -184,7 +184,7 @@ struct JointRec {
 #define JF_ENABLE_MOTOR 4u
 #define JF_HAS_PARAMS 8u
 #define JF_DEAD 0x80000000u
-#define JEXT_STRIDE 24 // long parameter table of a joint (slider: 22 values)
+#define JEXT_STRIDE 84 // long parameter table of a joint (slider: 22 values, 6-DOF: 3 x 28)
 
 // Per-step joint data written by k_joint_setup (the Jacobian diagonals of BradotJacobianEntry3D and
 // everything about the pivots / axes that stays constant while the solver sweeps).
@@ -197,6 +197,20 @@ struct __align__(16) JointSetup {
     float4 axis_b;     // hinge axis of B in world ; w = limit sign (0 = limit not violated)
     float4 lim;        // hinge: limit correction, accumulated limit impulse (cleared by the setup), motor target velocity, motor max impulse
     float4 prm;        // pin: bias, damping, impulse clamp ; hinge: bias, relaxation, limit bias
+};
+
+// Per-step data of a generic 6-DOF joint, beside its JointSetup (pa / pb = anchor minus origin A / B): k_joint_setup decides
+// which of the six axes act this step and with what values (bradot_generic_6dof_joint_3d.cpp:316-370 and the tests the
+// two solve routines make on constant data, :86-96, :186-206); the solver keeps the accumulated impulses in it.
+struct __align__(16) G6Setup {
+    float4 lin_a[3];  // axis xyz, 1 / Jacobian diagonal
+    float4 lin_b[3];  // depth (limit taken off), softness, restitution, damping
+    float4 lin_acc;   // accumulated impulses xyz ; w = bits: 2 per axis (0 skip, 1 lower clamp 0, 2 upper clamp 0, 3 no clamp)
+    float4 ang_a[3];  // axis xyz, 1 / Jacobian diagonal
+    float4 ang_b[3];  // target velocity, max impulse (force * dt), softness, damping
+    float4 ang_c;     // 1 + bounce xyz ; w = bits: 1 per axis (acts)
+    float4 ang_acc;   // accumulated impulses xyz
+    float4 pad;
 };
 
 struct Stats {
@@ -235,6 +249,8 @@ struct bpc_context {
     uint32_t stage_steps = 0;
     DevBuf<JointRec> d_joints;
     DevBuf<JointSetup> jsetup;
+    DevBuf<G6Setup> jsetup6; // one per joint, present once a 6-DOF joint exists
+    bool have_g6dof = false;
     DevBuf<uint32_t> a_range_cur; // same for the current pair list (vertex-centric island pass)
     DevBuf<uint32_t> a_range; // [2 * n_bodies]: begin / end of each body's run (as A) in the previous pair list
     DevBuf<uint32_t> io_slots; // body indices of a gather / scatter call

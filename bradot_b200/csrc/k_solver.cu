@@ -10,6 +10,7 @@
 
 #include <algorithm>
 
+#include "../../include/bradot_physics_cuda.h"
 #include "np_segment.cuh"
 namespace cg = cooperative_groups;
 
@@ -44,6 +45,7 @@ struct SvArgs {
     size_t sc_stride;
     const JointRec *joints;
     JointSetup *jsetup; // the solver keeps a hinge's accumulated limit impulse in it
+    G6Setup *jsetup6;   // 6-DOF joints, by joint index (null without such joints)
     uint32_t max_priority;
     // solver bins (k_solve_bins): per bin "fits one CTA", lowest / highest body, offsets of its colour runs
     const uint32_t *bin_ok, *bin_lo, *bin_hi, *bin_base;
@@ -513,7 +515,9 @@ __device__ __forceinline__ float jac_diag_inv(const M3 &w2a, const M3 &w2b, V3 r
 struct JsArgs {
     uint32_t n;
     const JointRec *joints;
-    const float *jext; // long parameter tables (sliders), JEXT_STRIDE per joint; null without such joints
+    const float *jext; // long parameter tables (sliders, 6-DOF), JEXT_STRIDE per joint; null without such joints
+    float dt;
+    G6Setup *out6;     // per-step data of the 6-DOF joints, one per joint; null without such joints
     JointSetup *out;
     const BodyXf *xf;
     const BodyMassW *massw;
@@ -659,6 +663,106 @@ __global__ void __launch_bounds__(128) k_joint_setup(JsArgs a) {
         s.axis_b = v4(twistAxis, kTwist);
         s.lim = make_float4(swingCorrection, 0.f, twistCorrection, 0.f); // corrections; accumulated swing / twist limit impulses
         s.prm = make_float4(0.3f, jr.prm[4], jr.prm[2], 0.f);             // tau (fixed, :208), relaxation, bias
+    } else if (jr.type == 4) {
+        // generic 6-DOF (joints/bradot_generic_6dof_joint_3d.cpp:316-370; calculateAngleInfo :210-246, calcAnchorPos :437-449,
+        // testLimitValue :64-84): which of the three linear and three angular axes act this step, and with what values
+        const float *gp = a.jext + (size_t)j * JEXT_STRIDE;
+        M3 fa(V3(jr.fa[0], jr.fa[1], jr.fa[2]), V3(jr.fa[3], jr.fa[4], jr.fa[5]), V3(jr.fa[6], jr.fa[7], jr.fa[8]));
+        M3 fb(V3(jr.fb[0], jr.fb[1], jr.fb[2]), V3(jr.fb[3], jr.fb[4], jr.fb[5]), V3(jr.fb[6], jr.fb[7], jr.fb[8]));
+        M3 ba = XA.b * fa, bb = XB.b * fb;
+        M3 rel = inverse(bb) * ba;
+        // Basis::get_euler(EulerOrder::XYZ), core/math/basis.cpp:458-493
+        V3 euler;
+        {
+            float sy = rel.r[0].z;
+            if (sy < (1.0f - (float)BPC_CMP_EPSILON)) {
+                if (sy > -(1.0f - (float)BPC_CMP_EPSILON)) {
+                    if (rel.r[1].x == 0 && rel.r[0].y == 0 && rel.r[1].z == 0 && rel.r[2].y == 0 && rel.r[1].y == 1) {
+                        euler = V3(0.f, atan2f(rel.r[0].z, rel.r[0].x), 0.f);
+                    } else {
+                        euler.x = atan2f(-rel.r[1].z, rel.r[2].z);
+                        euler.y = asinf(sy);
+                        euler.z = atan2f(-rel.r[0].y, rel.r[0].x);
+                    }
+                } else {
+                    euler = V3(atan2f(rel.r[2].y, rel.r[1].y), (float)(-3.14159265358979323846 / 2.0), 0.f);
+                }
+            } else {
+                euler = V3(atan2f(rel.r[2].y, rel.r[1].y), (float)(3.14159265358979323846 / 2.0), 0.f);
+            }
+        }
+        V3 axis0(bb.r[0].x, bb.r[1].x, bb.r[2].x), axis2(ba.r[0].z, ba.r[1].z, ba.r[2].z);
+        V3 cax[3];
+        cax[1] = cross(axis2, axis0);
+        cax[0] = cross(cax[1], axis2);
+        cax[2] = cross(axis0, cax[1]);
+        float weight = (imB == 0.0f) ? 1.0f : imA / (imA + imB);
+        V3 anchor = pivA * weight + pivB * (1.0f - weight);
+        rel1 = anchor - XA.o - comA;
+        rel2 = anchor - XB.o - comB;
+        G6Setup g;
+        memset(&g, 0, sizeof(g));
+        uint32_t lin_bits = 0, ang_bits = 0;
+        const float eul[3] = { euler.x, euler.y, euler.z };
+        for (int i = 0; i < 3; i++) {
+            const float *q = gp + i * BPC_G6DOF_AXIS_STRIDE;
+            // linear axis i: enabled and upper >= lower; the limit tests of solveLinearAxis work on constant data
+            if (q[22] != 0.f && q[1] >= q[0]) {
+                V3 nw(comp(ba.r[0], i), comp(ba.r[1], i), comp(ba.r[2], i)); // m_useLinearReferenceFrameA is always true (server :1518)
+                float depth = -dot(pivA - pivB, nw);
+                uint32_t mode = 3u;
+                if (q[0] < q[1]) {
+                    if (depth > q[1]) {
+                        depth -= q[1];
+                        mode = 1u;
+                    } else if (depth < q[0]) {
+                        depth -= q[0];
+                        mode = 2u;
+                    } else {
+                        mode = 0u;
+                    }
+                }
+                lin_bits |= mode << (2 * i);
+                g.lin_a[i] = v4(nw, jac_diag_inv(w2a, w2b, rel1, rel2, nw, iiA, imA, iiB, imB));
+                g.lin_b[i] = make_float4(depth, q[2], q[3], q[4]);
+            }
+            // angular axis i: limit enabled, and (motor or limit violated)
+            if (q[23] != 0.f) {
+                int current = 0;
+                float err = 0.f;
+                if (!(q[10] > q[11])) {
+                    if (eul[i] < q[10]) {
+                        current = 1;
+                        err = eul[i] - q[10];
+                    } else if (eul[i] > q[11]) {
+                        current = 2;
+                        err = eul[i] - q[11];
+                    }
+                }
+                if (q[26] != 0.f || current != 0) {
+                    float target = q[17], max_force = q[18];
+                    if (current != 0) {
+                        target = -q[16] * err / a.dt;
+                        max_force = q[15];
+                    }
+                    max_force *= a.dt;
+                    V3 aJ = xform(w2a, cax[i]), bJ = xform(w2b, -cax[i]);
+                    V3 m0(iiA.x * aJ.x, iiA.y * aJ.y, iiA.z * aJ.z), m1(iiB.x * bJ.x, iiB.y * bJ.y, iiB.z * bJ.z);
+                    float adiag = dot(m0, aJ) + dot(m1, bJ);
+                    g.ang_a[i] = v4(cax[i], 1.0f / adiag);
+                    g.ang_b[i] = make_float4(target, max_force, q[12], q[13]);
+                    ang_bits |= 1u << i;
+                }
+            }
+        }
+        g.ang_c = make_float4(1 + gp[14], 1 + gp[BPC_G6DOF_AXIS_STRIDE + 14], 1 + gp[2 * BPC_G6DOF_AXIS_STRIDE + 14], __uint_as_float(ang_bits));
+        g.lin_acc.w = __uint_as_float(lin_bits);
+        a.out6[j] = g;
+        memset(&s, 0, sizeof(s));
+        s.pa = v4(anchor - XA.o, __uint_as_float(flags));
+        s.pb = v4(anchor - XB.o, 0.f);
+        a.out[j] = s;
+        return;
     } else if (jr.type == 3) {
         // slider (joints/bradot_slider_joint_3d.cpp:74-137, testLinLimits :298-316, testAngLimits :320-337): the rows are the
         // axes of frame A in the world, the pivot of A is projected on the slider axis, the parameters of the branch that
@@ -854,6 +958,58 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
             V3 impulse = twistAxis * impulseMag;
             if (dynA) A.ang += xform(A.iinv, impulse);
             if (dynB) B.ang += xform(B.iinv, -impulse);
+        }
+    } else if (type == 4) { // generic 6-DOF (joints/bradot_generic_6dof_joint_3d.cpp:372-417; solveLinearAxis :159-218, solveAngularLimits :86-155)
+        G6Setup &g = a.jsetup6[inf.w];
+        const uint32_t lin_bits = __float_as_uint(g.lin_acc.w), ang_bits = __float_as_uint(g.ang_c.w);
+        float lacc[3] = { g.lin_acc.x, g.lin_acc.y, g.lin_acc.z };
+        for (int i = 0; i < 3; i++) {
+            uint32_t mode = (lin_bits >> (2 * i)) & 3u;
+            if (!mode) continue;
+            float4 la = g.lin_a[i], lb = g.lin_b[i];
+            V3 axis = f4v(la);
+            V3 vel = (A.lin + cross(A.ang, pA - A.com)) - (B.lin + cross(B.ang, pB - B.com));
+            float rel_vel = dot(axis, vel);
+            float lo = (mode == 1u) ? 0.f : -1e30f, hi = (mode == 2u) ? 0.f : 1e30f;
+            float normalImpulse = lb.y * (lb.z * lb.x / a.dt - lb.w * rel_vel) * la.w;
+            float old = lacc[i];
+            float sum = old + normalImpulse;
+            lacc[i] = sum > hi ? 0.f : (sum < lo ? 0.f : sum);
+            normalImpulse = lacc[i] - old;
+            V3 iv = axis * normalImpulse;
+            if (dynA) apply_impulse(A, iv, pA);
+            if (dynB) apply_impulse(B, -iv, pB);
+        }
+        if (lin_bits) {
+            g.lin_acc.x = lacc[0];
+            g.lin_acc.y = lacc[1];
+            g.lin_acc.z = lacc[2];
+        }
+        float aacc[3] = { g.ang_acc.x, g.ang_acc.y, g.ang_acc.z };
+        const float bounce1[3] = { g.ang_c.x, g.ang_c.y, g.ang_c.z };
+        for (int i = 0; i < 3; i++) {
+            if (!((ang_bits >> i) & 1u)) continue;
+            float4 aa = g.ang_a[i], ab = g.ang_b[i];
+            V3 axis = f4v(aa);
+            float rel_vel = dot(axis, A.ang - B.ang);
+            float motor_relvel = ab.z * (ab.x - ab.w * rel_vel);
+            if (is_zero_approx(motor_relvel)) continue;
+            float unclipped = bounce1[i] * motor_relvel * aa.w;
+            float clipped;
+            if (unclipped > 0.0f) clipped = unclipped > ab.y ? ab.y : unclipped;
+            else clipped = unclipped < -ab.y ? -ab.y : unclipped;
+            float old = aacc[i];
+            float sum = old + clipped;
+            aacc[i] = sum > 1e30f ? 0.f : (sum < -1e30f ? 0.f : sum);
+            clipped = aacc[i] - old;
+            V3 motorImp = clipped * axis;
+            if (dynA) A.ang += xform(A.iinv, motorImp);
+            if (dynB) B.ang += xform(B.iinv, -motorImp);
+        }
+        if (ang_bits) {
+            g.ang_acc.x = aacc[0];
+            g.ang_acc.y = aacc[1];
+            g.ang_acc.z = aacc[2];
         }
     } else if (type == 3) { // slider (joints/bradot_slider_joint_3d.cpp:141-275; its motors cannot be switched on through the server)
         V3 vel = (A.lin + cross(A.ang, pA - A.com)) - (B.lin + cross(B.ang, pB - B.com));
@@ -1191,6 +1347,16 @@ int bpc_launch_joint_setup(bpc_context *ctx, float dt) {
     a.joints = ctx->d_joints.p;
     a.jext = ctx->h_jext.empty() ? nullptr : ctx->d_jext.p;
     a.out = ctx->jsetup.p;
+    a.out6 = nullptr;
+    if (ctx->have_g6dof) {
+        ctx->jsetup6.reserve(nj, false, ctx->stream);
+        if (!ctx->jsetup6.p) {
+            ctx->err = "joints: out of device memory";
+            return -1;
+        }
+        a.out6 = ctx->jsetup6.p;
+    }
+    a.dt = dt;
     a.xf = ctx->xf.p;
     a.massw = ctx->massw.p;
     a.props = ctx->props.p;
@@ -1250,6 +1416,7 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     a.sc_stride = maxc;
     a.joints = ctx->d_joints.p;
     a.jsetup = ctx->jsetup.p;
+    a.jsetup6 = ctx->have_g6dof ? ctx->jsetup6.p : nullptr;
     a.report_cap = ctx->n_reporting ? ctx->report_cap.p : nullptr;
     a.report_ofs = ctx->report_ofs.p;
     a.report_count = ctx->report_count.p;

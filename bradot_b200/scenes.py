@@ -16,7 +16,7 @@ import numpy as np
 
 SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONVEX, SHAPE_CONCAVE, SHAPE_HEIGHTMAP = range(9)
 MODE_STATIC, MODE_KINEMATIC, MODE_RIGID, MODE_RIGID_LINEAR = range(4)
-JOINT_PIN, JOINT_HINGE, JOINT_CONE_TWIST, JOINT_SLIDER = 0, 1, 2, 3
+JOINT_PIN, JOINT_HINGE, JOINT_CONE_TWIST, JOINT_SLIDER, JOINT_6DOF = 0, 1, 2, 3, 4
 
 SHAPE_DT = np.dtype([("type", "<u4"), ("p", "<f4", 4), ("vert_ofs", "<u4"), ("vert_cnt", "<u4"), ("pad", "<u4")])
 BODY_DT = np.dtype([
@@ -621,6 +621,78 @@ def slider_rigs(n_rigs=18, seed=11):
                 else:           # only some of them: the linear limits and the angular block
                     sc.set_joint_params(j, 0, v[0:2])
                     sc.set_joint_params(j, 11, v[11:22])
+    return sc
+
+
+def g6dof_axis_defaults():
+    """One axis block of a 6-DOF joint's long parameter table (include/bradot_physics_cuda.h): 22 G6DOFJointAxisParam values,
+    6 flags; the members of the reference's joint as constructed."""
+    q = np.zeros(28, np.float32)
+    q[2], q[3], q[4] = 0.7, 0.5, 1.0
+    q[10], q[11], q[12], q[13], q[15], q[16], q[18] = -1e30, 1e30, 0.5, 1.0, 300.0, 0.5, 0.1
+    q[22] = 1.0
+    return q
+
+
+def sixdof_rigs(n_rigs=18, seed=13):
+    """Generic 6-DOF joints: rig r is a static anchor, a box on it and a second box on the first, both by 6-DOF joints in turned
+    frames; no collisions.  r % 3 == 0: every default (three locked linear axes, no angular limits).  r % 3 == 1: x limited
+    to a range that is hit, y locked, z free; angular limits on x and y narrow enough to be violated, z free with its motor
+    running.  r % 3 == 2: own softness / restitution / damping / ERP values, a limit force small enough to clip, bounce, the
+    y linear limit switched off.  Rigs with r % 4 == 3 run at solver priority 2."""
+    sc = Scene(name="sixdof_rigs_%d" % n_rigs)
+    anchor = sc.add_shape(SHAPE_BOX, (0.1, 0.1, 0.1))
+    link = sc.add_shape(SHAPE_BOX, (0.3, 0.12, 0.2))
+    rng = np.random.default_rng(seed)
+    for r in range(n_rigs):
+        x0 = r * 8.0
+        xa = IDENT12.copy()
+        xa[9], xa[10] = x0, 10.0
+        a = sc.add_bodies(1, mode=MODE_STATIC, shape=anchor, xf=xa, layer=0, mask=0)
+        xf = np.tile(IDENT12, (2, 1))
+        xf[:, 9] = x0 + np.array([0.5, 1.3])
+        xf[:, 10] = 10.0 - np.array([0.3, 0.7])
+        lin = rng.uniform(-1.5, 1.5, (2, 3)).astype(np.float32)
+        ang = rng.uniform(-2.5, 2.5, (2, 3)).astype(np.float32)
+        first = sc.add_bodies(2, shape=link, xf=xf, mass=0.6 + 0.3 * (r % 3), layer=0, mask=0, linvel=lin, angvel=ang, flags=0)
+        prio = 2 if r % 4 == 3 else 0
+        for k, (ba, bb) in enumerate(((a, first), (first, first + 1))):
+            th, ph = 0.25 * ((r + k) % 4), 0.3 * ((r + 2 * k) % 3)
+            c, s, c2, s2 = np.cos(th), np.sin(th), np.cos(ph), np.sin(ph)
+            rz = np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]])
+            rx = np.array([[1, 0, 0], [0, c2, -s2], [0, s2, c2]])
+            ry = np.array([[np.cos(0.2 * k), 0, np.sin(0.2 * k)], [0, 1, 0], [-np.sin(0.2 * k), 0, np.cos(0.2 * k)]])
+            fa, fb = IDENT12.copy(), IDENT12.copy()
+            fa[0:9] = (rz @ rx).reshape(-1)
+            fb[0:9] = (rz @ rx @ ry).reshape(-1)
+            fa[9:12] = (0.4, -0.2, 0.0)
+            fb[9:12] = (-0.35, 0.1, 0.05)
+            j = sc.add_joints(1, type=JOINT_6DOF, body_a=ba, body_b=bb, flags=JOINT_NO_COLLIDE, fa=fa, fb=fb, priority=prio)
+            if r % 3 == 0:
+                continue
+            for ax in range(3):
+                q = g6dof_axis_defaults()
+                if r % 3 == 1:
+                    if ax == 0:
+                        q[0], q[1] = -0.05, 0.08
+                    elif ax == 2:
+                        q[0], q[1] = 1.0, -1.0
+                    q[23] = 1.0
+                    if ax == 0:
+                        q[10], q[11] = -0.1, 0.15
+                    elif ax == 1:
+                        q[10], q[11] = -0.05, 0.1
+                    else:
+                        q[10], q[11] = 1.0, -1.0
+                        q[26], q[17] = 1.0, 1.5
+                else:
+                    q[0], q[1] = (-0.03, 0.04) if ax != 1 else (0.0, 0.0)
+                    q[2], q[3], q[4] = 0.8, 0.6 - 0.1 * ax, 0.9
+                    q[22] = 0.0 if ax == 1 else 1.0
+                    q[23] = 1.0
+                    q[10], q[11] = -0.08 - 0.02 * ax, 0.06
+                    q[12], q[13], q[14], q[15], q[16] = 0.6, 0.9, 0.2, 2.0 + ax, 0.4
+                sc.set_joint_params(j, ax * 28, q)
     return sc
 
 

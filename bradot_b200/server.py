@@ -348,7 +348,7 @@ class PhysicsServerCUDA:
         v = np.ascontiguousarray(values, np.float32).reshape(-1)
         self._check(self.lib.bpc_joint_params_write(self.ctx, int(joint), int(first), len(v), _ptr(v)))
 
-    def joint_params_read(self, joint, first=0, n=22):
+    def joint_params_read(self, joint, first=0, n=22):   # (a 6-DOF joint has 84: three blocks of 28)
         v = np.zeros(n, np.float32)
         self._check(self.lib.bpc_joint_params_read(self.ctx, int(joint), int(first), int(n), _ptr(v)))
         return v

@@ -1418,7 +1418,7 @@ void BradotPhysicsServerCUDA::_fill_joint_desc(const Joint *p_joint, bpc_joint_d
 	const Joint *j = p_joint;
 	const Body *a = body_owner.get_or_null(j->a), *b = body_owner.get_or_null(j->b);
 	r_desc = {};
-	r_desc.type = j->type == JOINT_TYPE_PIN ? BPC_JOINT_PIN : (j->type == JOINT_TYPE_HINGE ? BPC_JOINT_HINGE : (j->type == JOINT_TYPE_SLIDER ? BPC_JOINT_SLIDER : BPC_JOINT_CONE_TWIST));
+	r_desc.type = j->type == JOINT_TYPE_PIN ? BPC_JOINT_PIN : (j->type == JOINT_TYPE_HINGE ? BPC_JOINT_HINGE : (j->type == JOINT_TYPE_SLIDER ? BPC_JOINT_SLIDER : (j->type == JOINT_TYPE_6DOF ? BPC_JOINT_6DOF : BPC_JOINT_CONE_TWIST)));
 	r_desc.body_a = a ? a->slot : 0;
 	r_desc.body_b = b ? b->slot : 0;
 	r_desc.flags = (j->disable_collisions ? 1 : 0) | 8; // parameters are always given
@@ -1428,7 +1428,7 @@ void BradotPhysicsServerCUDA::_fill_joint_desc(const Joint *p_joint, bpc_joint_d
 		for (int k = 0; k < 3; k++) {
 			r_desc.params[k] = j->pin_params[k];
 		}
-	} else if (j->type == JOINT_TYPE_SLIDER) {
+	} else if (j->type == JOINT_TYPE_SLIDER || j->type == JOINT_TYPE_6DOF) {
 		// its values go through bpc_joint_params_write
 	} else if (j->type == JOINT_TYPE_CONE_TWIST) {
 		for (int k = 0; k < CONE_TWIST_MAX + 1; k++) {
@@ -1641,6 +1641,116 @@ real_t BradotPhysicsServerCUDA::slider_joint_get_param(RID p_joint, SliderJointP
 	ERR_FAIL_COND_V(joint->type != JOINT_TYPE_SLIDER, 0);
 	ERR_FAIL_INDEX_V((int)p_param, (int)SLIDER_JOINT_MAX, 0);
 	return joint->slider_params[p_param];
+}
+
+// joint_make_generic_6dof / generic_6dof_joint_* (bradot_physics_server_3d.cpp:1501-1555; the joint itself:
+// joints/bradot_generic_6dof_joint_3d.cpp).  The table holds the joint's members; set_param / get_param map the server's
+// parameters on them exactly as the reference's switch does (:451-601) -- its quirks included: ANGULAR_MOTOR_FORCE_LIMIT
+// writes the LIMIT force and reads the motor force, linear motors and all springs are ignored and read as 0.
+void BradotPhysicsServerCUDA::joint_make_generic_6dof(RID p_joint, RID p_body_A, const Transform3D &p_local_frame_A, RID p_body_B, const Transform3D &p_local_frame_B) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body_A));
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body_B));
+	joint_clear(p_joint);
+	joint->type = JOINT_TYPE_6DOF;
+	joint->a = p_body_A;
+	joint->b = p_body_B;
+	joint->fa = p_local_frame_A;
+	joint->fb = p_local_frame_B;
+	for (int ax = 0; ax < 3; ax++) {
+		float *q = joint->g6_params + ax * BPC_G6DOF_AXIS_STRIDE;
+		for (int k = 0; k < BPC_G6DOF_AXIS_STRIDE; k++) {
+			q[k] = 0.0f;
+		}
+		q[G6DOF_JOINT_LINEAR_LIMIT_SOFTNESS] = 0.7f;
+		q[G6DOF_JOINT_LINEAR_RESTITUTION] = 0.5f;
+		q[G6DOF_JOINT_LINEAR_DAMPING] = 1.0f;
+		q[G6DOF_JOINT_ANGULAR_LOWER_LIMIT] = -1e30f;
+		q[G6DOF_JOINT_ANGULAR_UPPER_LIMIT] = 1e30f;
+		q[G6DOF_JOINT_ANGULAR_LIMIT_SOFTNESS] = 0.5f;
+		q[G6DOF_JOINT_ANGULAR_DAMPING] = 1.0f;
+		q[G6DOF_JOINT_ANGULAR_FORCE_LIMIT] = 300.0f;
+		q[G6DOF_JOINT_ANGULAR_ERP] = 0.5f;
+		q[G6DOF_JOINT_ANGULAR_MOTOR_FORCE_LIMIT] = 0.1f;
+		q[G6DOF_JOINT_MAX + G6DOF_JOINT_FLAG_ENABLE_LINEAR_LIMIT] = 1.0f;
+	}
+	joint->pending = true;
+	pending_joints.push_back(joint);
+}
+
+static int _g6_slot(PhysicsServer3D::G6DOFJointAxisParam p_param, bool p_write) {
+	switch (p_param) {
+		case PhysicsServer3D::G6DOF_JOINT_LINEAR_LOWER_LIMIT:
+		case PhysicsServer3D::G6DOF_JOINT_LINEAR_UPPER_LIMIT:
+		case PhysicsServer3D::G6DOF_JOINT_LINEAR_LIMIT_SOFTNESS:
+		case PhysicsServer3D::G6DOF_JOINT_LINEAR_RESTITUTION:
+		case PhysicsServer3D::G6DOF_JOINT_LINEAR_DAMPING:
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_LOWER_LIMIT:
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_UPPER_LIMIT:
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_LIMIT_SOFTNESS:
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_DAMPING:
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_RESTITUTION:
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_FORCE_LIMIT:
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_ERP:
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_MOTOR_TARGET_VELOCITY:
+			return (int)p_param;
+		case PhysicsServer3D::G6DOF_JOINT_ANGULAR_MOTOR_FORCE_LIMIT:
+			return p_write ? (int)PhysicsServer3D::G6DOF_JOINT_ANGULAR_FORCE_LIMIT : (int)p_param;
+		default:
+			return -1; // not implemented in the reference backend
+	}
+}
+
+void BradotPhysicsServerCUDA::generic_6dof_joint_set_param(RID p_joint, Vector3::Axis p_axis, G6DOFJointAxisParam p_param, real_t p_value) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND(joint->type != JOINT_TYPE_6DOF);
+	ERR_FAIL_INDEX((int)p_axis, 3);
+	int slot = _g6_slot(p_param, true);
+	if (slot < 0) {
+		return;
+	}
+	int idx = (int)p_axis * BPC_G6DOF_AXIS_STRIDE + slot;
+	joint->g6_params[idx] = p_value;
+	if (joint->handle >= 0) {
+		ERR_FAIL_COND_MSG(bpc_joint_params_write(ctx, joint->handle, idx, 1, &joint->g6_params[idx]) < 0, bpc_last_error(ctx));
+	}
+}
+
+real_t BradotPhysicsServerCUDA::generic_6dof_joint_get_param(RID p_joint, Vector3::Axis p_axis, G6DOFJointAxisParam p_param) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, 0);
+	ERR_FAIL_COND_V(joint->type != JOINT_TYPE_6DOF, 0);
+	ERR_FAIL_INDEX_V((int)p_axis, 3, 0);
+	int slot = _g6_slot(p_param, false);
+	return slot < 0 ? real_t(0) : real_t(joint->g6_params[(int)p_axis * BPC_G6DOF_AXIS_STRIDE + slot]);
+}
+
+void BradotPhysicsServerCUDA::generic_6dof_joint_set_flag(RID p_joint, Vector3::Axis p_axis, G6DOFJointAxisFlag p_flag, bool p_enable) {
+	Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL(joint);
+	ERR_FAIL_COND(joint->type != JOINT_TYPE_6DOF);
+	ERR_FAIL_INDEX((int)p_axis, 3);
+	if (p_flag != G6DOF_JOINT_FLAG_ENABLE_LINEAR_LIMIT && p_flag != G6DOF_JOINT_FLAG_ENABLE_ANGULAR_LIMIT && p_flag != G6DOF_JOINT_FLAG_ENABLE_MOTOR) {
+		return; // not implemented in the reference backend
+	}
+	int idx = (int)p_axis * BPC_G6DOF_AXIS_STRIDE + (int)G6DOF_JOINT_MAX + (int)p_flag;
+	joint->g6_params[idx] = p_enable ? 1.0f : 0.0f;
+	if (joint->handle >= 0) {
+		ERR_FAIL_COND_MSG(bpc_joint_params_write(ctx, joint->handle, idx, 1, &joint->g6_params[idx]) < 0, bpc_last_error(ctx));
+	}
+}
+
+bool BradotPhysicsServerCUDA::generic_6dof_joint_get_flag(RID p_joint, Vector3::Axis p_axis, G6DOFJointAxisFlag p_flag) const {
+	const Joint *joint = joint_owner.get_or_null(p_joint);
+	ERR_FAIL_NULL_V(joint, false);
+	ERR_FAIL_COND_V(joint->type != JOINT_TYPE_6DOF, false);
+	ERR_FAIL_INDEX_V((int)p_axis, 3, false);
+	if (p_flag != G6DOF_JOINT_FLAG_ENABLE_LINEAR_LIMIT && p_flag != G6DOF_JOINT_FLAG_ENABLE_ANGULAR_LIMIT && p_flag != G6DOF_JOINT_FLAG_ENABLE_MOTOR) {
+		return false;
+	}
+	return joint->g6_params[(int)p_axis * BPC_G6DOF_AXIS_STRIDE + (int)G6DOF_JOINT_MAX + (int)p_flag] != 0.0f;
 }
 
 // joint_make_cone_twist / cone_twist_joint_*_param (bradot_physics_server_3d.cpp:1461-1499; the joint itself:
@@ -2289,6 +2399,8 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 				uploaded[i]->pending = false;
 				if (uploaded[i]->type == JOINT_TYPE_SLIDER) {
 					ERR_FAIL_COND_MSG(bpc_joint_params_write(ctx, first + i, 0, SLIDER_JOINT_MAX, uploaded[i]->slider_params) < 0, bpc_last_error(ctx));
+				} else if (uploaded[i]->type == JOINT_TYPE_6DOF) {
+					ERR_FAIL_COND_MSG(bpc_joint_params_write(ctx, first + i, 0, BPC_G6DOF_PARAMS, uploaded[i]->g6_params) < 0, bpc_last_error(ctx));
 				}
 			}
 		}

@@ -6,7 +6,7 @@
 // Implemented by hand: what a scene of RigidBody3D / StaticBody3D nodes needs -- spaces (create, activate, parameters, free),
 // world-boundary / sphere / box / capsule / convex shapes, bodies with one shape (every setter also after the body is in a
 // space; state-sync and force-integration callbacks; PhysicsDirectBodyState3D; impulses, forces, constant forces; axis
-// locks; collision exceptions; free), pin, hinge, slider and cone-twist joints with their parameters, flags and solver priority, step, stats,
+// locks; collision exceptions; free), pin, hinge, slider, cone-twist and 6-DOF joints with their parameters, flags and solver priority, step, stats,
 // PhysicsDirectSpaceState3D queries.  Every other pure virtual of the interface gets a generated default override
 // (engine_module/gen_stubs.py) that logs once and returns the type's default, which is how the reference answers an
 // invalid RID.
@@ -165,6 +165,9 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		// SliderJointParam order; the members of BradotSliderJoint3D as constructed (joints/bradot_slider_joint_3d.h:80-110)
 		float slider_params[SLIDER_JOINT_MAX] = { -1.0f, 1.0f, 1.0f, 0.7f, 1.0f, 1.0f, 0.7f, 0.0f, 1.0f, 0.7f, 1.0f,
 			0.0f, 0.0f, 1.0f, 0.7f, 1.0f, 1.0f, 0.7f, 0.0f, 1.0f, 0.7f, 1.0f };
+		// generic 6-DOF: per axis the G6DOFJointAxisParam values then the flags, as the members of the reference's joint
+		// stand after construction (joints/bradot_generic_6dof_joint_3d.h:67-112); filled by joint_make_generic_6dof
+		float g6_params[BPC_G6DOF_PARAMS] = {};
 		bool pending = false;
 		int handle = -1;
 	};
@@ -378,6 +381,11 @@ public:
 	virtual void joint_make_slider(RID p_joint, RID p_body_A, const Transform3D &p_local_frame_A, RID p_body_B, const Transform3D &p_local_frame_B) override;
 	virtual void slider_joint_set_param(RID p_joint, SliderJointParam p_param, real_t p_value) override;
 	virtual real_t slider_joint_get_param(RID p_joint, SliderJointParam p_param) const override;
+	virtual void joint_make_generic_6dof(RID p_joint, RID p_body_A, const Transform3D &p_local_frame_A, RID p_body_B, const Transform3D &p_local_frame_B) override;
+	virtual void generic_6dof_joint_set_param(RID p_joint, Vector3::Axis p_axis, G6DOFJointAxisParam p_param, real_t p_value) override;
+	virtual real_t generic_6dof_joint_get_param(RID p_joint, Vector3::Axis p_axis, G6DOFJointAxisParam p_param) const override;
+	virtual void generic_6dof_joint_set_flag(RID p_joint, Vector3::Axis p_axis, G6DOFJointAxisFlag p_flag, bool p_enable) override;
+	virtual bool generic_6dof_joint_get_flag(RID p_joint, Vector3::Axis p_axis, G6DOFJointAxisFlag p_flag) const override;
 	virtual void joint_make_cone_twist(RID p_joint, RID p_body_A, const Transform3D &p_local_frame_A, RID p_body_B, const Transform3D &p_local_frame_B) override;
 	virtual void cone_twist_joint_set_param(RID p_joint, ConeTwistJointParam p_param, real_t p_value) override;
 	virtual real_t cone_twist_joint_get_param(RID p_joint, ConeTwistJointParam p_param) const override;

@@ -288,6 +288,20 @@ int main(int argc, char **argv) {
 					ps->slider_joint_set_param(jr, (PhysicsServer3D::SliderJointParam)(e.first + k), e.values[k]);
 				}
 			}
+		} else if (j.type == 4) {
+			ps->joint_make_generic_6dof(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
+			for (const ScnJointExt &e : sjext) {
+				for (uint32_t k = 0; e.joint == (uint32_t)joint_r.size() && k < e.count; k++) {
+					uint32_t idx = e.first + k, axis = idx / 28, prm = idx % 28;
+					if (prm < (uint32_t)PhysicsServer3D::G6DOF_JOINT_MAX) {
+						if (prm != (uint32_t)PhysicsServer3D::G6DOF_JOINT_ANGULAR_MOTOR_FORCE_LIMIT) {
+							ps->generic_6dof_joint_set_param(jr, (Vector3::Axis)axis, (PhysicsServer3D::G6DOFJointAxisParam)prm, e.values[k]);
+						}
+					} else {
+						ps->generic_6dof_joint_set_flag(jr, (Vector3::Axis)axis, (PhysicsServer3D::G6DOFJointAxisFlag)(prm - 22), e.values[k] != 0.0f);
+					}
+				}
+			}
 		} else if (j.type == 2) {
 			ps->joint_make_cone_twist(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
 			if (j.flags & 8) {

@@ -21,8 +21,10 @@ typedef struct bpc_context bpc_context;
 
 enum { BPC_SHAPE_WORLD_BOUNDARY = 0, BPC_SHAPE_SPHERE = 2, BPC_SHAPE_BOX = 3, BPC_SHAPE_CAPSULE = 4, BPC_SHAPE_CONVEX_POLYGON = 6 };
 enum { BPC_BODY_MODE_STATIC = 0, BPC_BODY_MODE_KINEMATIC = 1, BPC_BODY_MODE_RIGID = 2, BPC_BODY_MODE_RIGID_LINEAR = 3 };
-enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1, BPC_JOINT_CONE_TWIST = 2, BPC_JOINT_SLIDER = 3 };
+enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1, BPC_JOINT_CONE_TWIST = 2, BPC_JOINT_SLIDER = 3, BPC_JOINT_6DOF = 4 };
 #define BPC_SLIDER_PARAMS 22 /* PhysicsServer3D::SLIDER_JOINT_MAX */
+#define BPC_G6DOF_AXIS_STRIDE 28 /* per axis: PhysicsServer3D::G6DOF_JOINT_MAX (22) values, then G6DOF_JOINT_FLAG_MAX (6) flags */
+#define BPC_G6DOF_PARAMS 84
 
 /* Bulk body description; one record per body.  Same layout as the record of the neutral scene
  * file (bradot_b200/scenes.py BODY_DT).  Replaces the per-body call sequence body_create /
@@ -260,7 +262,13 @@ int bpc_joints_destroy(bpc_context *ctx, int first, int n);
  * PhysicsServer3D::SliderJointParam order (slider_joint_set_param / slider_joint_get_param,
  * P3D/joints/bradot_slider_joint_3d.cpp:349-479; defaults P3D/joints/bradot_slider_joint_3d.h:80-110, which a new slider
  * joint starts with -- its `params` and the `params holds values` flag are ignored).  Write / read `n` values starting at
- * parameter `first`.  Slider frames: the joint slides along the x axis of frame A. */
+ * parameter `first`.  Slider frames: the joint slides along the x axis of frame A.
+ * A generic 6-DOF joint (P3D/joints/bradot_generic_6dof_joint_3d.cpp) has 84 values: for each axis x, y, z a block of
+ * BPC_G6DOF_AXIS_STRIDE, the G6DOFJointAxisParam values first, then the G6DOFJointAxisFlag flags as 0 / 1.  The table holds the
+ * MEMBERS of the reference's joint (defaults bradot_generic_6dof_joint_3d.h:67-112: linear limits [0, 0] enabled, angular
+ * limits disabled): the entries the reference ignores (linear motors, springs) are ignored here, and
+ * ANGULAR_MOTOR_FORCE_LIMIT is the motor's force limit -- which the reference's own set_param never reaches (its case
+ * writes the LIMIT force, :497-499; the engine module mirrors that). */
 int bpc_joint_params_write(bpc_context *ctx, int joint, int first, int n, const float *values);
 int bpc_joint_params_read(bpc_context *ctx, int joint, int first, int n, float *values);
 int bpc_joint_count(bpc_context *ctx);

@@ -1036,6 +1036,8 @@ int main(int argc, char **argv) {
 			ps->joint_make_cone_twist(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		} else if (j.type == 3) {
 			ps->joint_make_slider(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
+		} else if (j.type == 4) {
+			ps->joint_make_generic_6dof(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		} else {
 			ps->joint_make_hinge(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		}
@@ -1046,6 +1048,20 @@ int main(int argc, char **argv) {
 			for (const ScnJointExt &e : sjext) {
 				for (uint32_t k = 0; e.joint == i && k < e.count; k++) {
 					ps->slider_joint_set_param(jr, (PhysicsServer3D::SliderJointParam)(e.first + k), e.values[k]);
+				}
+			}
+		} else if (j.type == 4) {
+			// blocks of 28 per axis: the G6DOFJointAxisParam values, then the flags (include/bradot_physics_cuda.h)
+			for (const ScnJointExt &e : sjext) {
+				for (uint32_t k = 0; e.joint == i && k < e.count; k++) {
+					uint32_t idx = e.first + k, axis = idx / 28, prm = idx % 28;
+					if (prm < (uint32_t)PhysicsServer3D::G6DOF_JOINT_MAX) {
+						if (prm != (uint32_t)PhysicsServer3D::G6DOF_JOINT_ANGULAR_MOTOR_FORCE_LIMIT) { // (that member cannot be reached through set_param)
+							ps->generic_6dof_joint_set_param(jr, (Vector3::Axis)axis, (PhysicsServer3D::G6DOFJointAxisParam)prm, e.values[k]);
+						}
+					} else {
+						ps->generic_6dof_joint_set_flag(jr, (Vector3::Axis)axis, (PhysicsServer3D::G6DOFJointAxisFlag)(prm - 22), e.values[k] != 0.0f);
+					}
 				}
 			}
 		} else if (j.flags & 8) {

@@ -450,6 +450,29 @@ def test_slider_joints_match_the_reference():
     ps.finish()
 
 
+def test_generic_6dof_joints_match_the_reference():
+    """Generic6DOFJoint3D (joints/bradot_generic_6dof_joint_3d.cpp:64-449): rigs on 6-DOF joints in turned frames -- locked, limited,
+    free and switched-off linear axes, violated angular limits (Euler XYZ of the relative frame), a running motor, clipped limit
+    forces, bounce; teacher-forced with the reference's sweep order, body state after the step within 1e-4.  The same rigs with
+    every default move differently."""
+    _need_oracle()
+    sc = scenes.sixdof_rigs()
+    assert (sc.joints["type"] == scenes.JOINT_6DOF).sum() == 36
+    _, dump = parity.run_oracle(sc, 80)
+    w = parity.teacher_forced(sc, 80, [1, 2, 5, 15, 30, 50, 79], dump=dump)
+    assert w["state"] < STATE_TOL, w
+    plain = scenes.sixdof_rigs()
+    plain.joint_ext = plain.joint_ext[:0]
+    ps = parity.new_server(plain, dump)
+    parity.load_state(ps, dump, 30)
+    ps.set_solve_order(parity.solve_order(dump, 31))
+    ps.step(sc.dt)
+    av = ps.bodies_read(server.FIELD_ANGULAR_VELOCITY)
+    assert parity.rel_err(av, dump[("bodies", 31)][:, 15:18], 1.0) > 1e-2
+    assert np.array_equal(ps.joint_params_read(0, 28, 28), scenes.g6dof_axis_defaults())
+    ps.finish()
+
+
 def test_cone_twist_joints_match_the_reference():
     """ConeTwistJoint3D (joints/bradot_cone_twist_joint_3d.cpp:67-279: swing ellipse and twist limits with accumulated, clamped
     impulses, the shortest-arc quaternion for the twist reference): chains whose links alternate hinges and cone-twist joints,
