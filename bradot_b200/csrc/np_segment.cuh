@@ -237,10 +237,97 @@ __device__ inline bool q_mesh_segment(const MeshPools &a, const MeshRec &mesh, V
     return collisions > 0;
 }
 
+// BradotHeightMapShape3D::intersect_segment (bradot_shape_3d.cpp:1950-2008) with _intersect_grid_segment (:1810-1948) and
+// _heightmap_cell_cull_segment (:1753-1772): a segment inside one cell tests that cell's two faces; any other walks the cells
+// under its flat projection in crossing order and returns the FIRST face hit in that order (front faces only on the
+// walk).  The reference's bounds chunks only skip cells the segment passes above or below; they are not kept here.
+// Pool layout of a height map: np_face.cuh (heights four to a float4, vert_cnt = width, face_cnt = depth).
+__device__ inline bool q_heightmap_segment(const MeshPools &a, const MeshRec &mesh, V3 from, V3 to, bool hit_back_faces, RayHit &h) {
+    const int width = (int)mesh.vert_cnt, depth = (int)mesh.face_cnt;
+    if (width < 2 || depth < 2) return false;
+    const float4 *hp = a.mverts + mesh.vert_ofs;
+    auto point_at = [&](int x, int z) -> V3 {
+        int i = z * width + x;
+        float4 h4 = hp[i >> 2];
+        float y = (i & 3) == 0 ? h4.x : (i & 3) == 1 ? h4.y : (i & 3) == 2 ? h4.z : h4.w;
+        return V3((float)((double)x - 0.5 * ((double)width - 1.0)), y, (float)((double)z - 0.5 * ((double)depth - 1.0)));
+    };
+    auto face_hit = [&](V3 v0, V3 v1, V3 v2, bool back) -> bool {
+        V3 res;
+        if (!q_triangle_segment(from, to, v0, v1, v2, res)) return false;
+        V3 normal = normalized(cross(v0 - v2, v0 - v1));
+        if (dot(normal, to - from) > 0) {
+            if (!back) return false;
+            normal = -normal;
+        }
+        h.point = res;
+        h.normal = normal;
+        return true;
+    };
+    auto cell_hit = [&](int x, int z, bool back) -> bool {
+        V3 v0 = point_at(x, z), v1 = point_at(x + 1, z), v2 = point_at(x, z + 1);
+        if (face_hit(v0, v1, v2, back)) return true;
+        return face_hit(v1, point_at(x + 1, z + 1), v2, back);
+    };
+    const V3 local_origin((float)(0.5 * (double)(width - 1)), 0.f, (float)(0.5 * (double)(depth - 1)));
+    V3 lb = from + local_origin, le = to + local_origin;
+    int begin_x = (int)floorf(lb.x), begin_z = (int)floorf(lb.z), end_x = (int)floorf(le.x), end_z = (int)floorf(le.z);
+    if (begin_x == end_x && begin_z == end_z) return cell_hit(max(min(begin_x, width - 2), 0), max(min(begin_z, depth - 2), 0), hit_back_faces);
+    V3 delta = to - from;
+    float len = length(delta);
+    if (len < (float)BPC_CMP_EPSILON) return false;
+    float fx = delta.x, fz = delta.z;
+    float len_flat = sqrtf(fx * fx + fz * fz);
+    if (len_flat < (float)BPC_CMP_EPSILON) {
+        fx = fz = 0.f;
+    } else {
+        fx /= len_flat;
+        fz /= len_flat;
+    }
+    const int x_step = (fx > (float)BPC_CMP_EPSILON) ? 1 : ((fx < -(float)BPC_CMP_EPSILON) ? -1 : 0);
+    const int z_step = (fz > (float)BPC_CMP_EPSILON) ? 1 : ((fz < -(float)BPC_CMP_EPSILON) ? -1 : 0);
+    const float infinite = 1e20f;
+    const float delta_x = (x_step != 0) ? 1.f / fabsf(fx) : infinite, delta_z = (z_step != 0) ? 1.f / fabsf(fz) : infinite;
+    float cross_x = infinite, cross_z = infinite;
+    if (x_step != 0) cross_x = (x_step == 1) ? (ceilf(lb.x) - lb.x) * delta_x : (lb.x - floorf(lb.x)) * delta_x;
+    if (z_step != 0) cross_z = (z_step == 1) ? (ceilf(lb.z) - lb.z) * delta_z : (lb.z - floorf(lb.z)) * delta_z;
+    int x = (int)floorf(lb.x), z = (int)floorf(lb.z);
+    if (is_zero_approx(cross_x)) { // the ray starts on a lane
+        cross_x += delta_x;
+        if (x_step == -1) x -= 1;
+    }
+    if (is_zero_approx(cross_z)) {
+        cross_z += delta_z;
+        if (z_step == -1) z -= 1;
+    }
+    int x_start = max(min(x, width - 2), 0), z_start = max(min(z, depth - 2), 0);
+    cross_x += delta_x * (float)x_step * (float)(x_start - x);
+    cross_z += delta_z * (float)z_step * (float)(z_start - z);
+    x = x_start;
+    z = z_start;
+    for (int guard = 0; guard < 2 * (width + depth) + 4; guard++) {
+        int cx = x, cz = z;
+        float dist;
+        if (cross_x < cross_z) {
+            x += x_step;
+            dist = cross_x;
+            cross_x += delta_x;
+        } else {
+            z += z_step;
+            dist = cross_z;
+            cross_z += delta_z;
+        }
+        if (dist > len_flat) return cell_hit(cx, cz, false);
+        if (cell_hit(cx, cz, false)) return true;
+        if (x < 0 || z < 0 || x >= width - 1 || z >= depth - 1) break;
+    }
+    return false;
+}
+
 __device__ inline bool q_shape_segment(const MeshPools &a, const QShape &s, V3 from, V3 to, RayHit &h, bool hit_back_faces = true) {
     switch (s.type) {
         case SH_CONCAVE: return q_mesh_segment(a, s.mesh, from, to, hit_back_faces, h);
-        case SH_HEIGHTMAP: return false; // the grid walk of BradotHeightMapShape3D::intersect_segment is not built: rays pass through height maps
+        case SH_HEIGHTMAP: return q_heightmap_segment(a, s.mesh, from, to, hit_back_faces, h);
         case SH_PLANE: { // Plane::intersects_segment
             V3 n(s.p.x, s.p.y, s.p.z);
             V3 segment = from - to;

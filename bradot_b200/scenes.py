@@ -487,6 +487,53 @@ def bullets(n=12):
     return sc
 
 
+def mesh_bullets(n=12):
+    """Continuous collision detection against static meshes: the bullets of bullets() fired at a wall made of two triangles
+    (a ConcavePolygonShape3D whose faces look at the bullets), at a second, two-sided one behind a gap in the first, and, from
+    above, at a height map.  Every second bullet has the CCD flag."""
+    sc = Scene(name="mesh_bullets")
+    sc.add_static_plane((0, 1, 0), -12.0)
+    quad = lambda x0, x1: np.array([[(x0, -3, 0), (x1, -3, 0), (x0, 3, 0)], [(x1, -3, 0), (x1, 3, 0), (x0, 3, 0)]], np.float32)   # normals -z
+    wall = sc.add_shape(SHAPE_CONCAVE, (0.0,), verts=quad(-3.0, 0.0).reshape(-1, 3))
+    wall2 = sc.add_shape(SHAPE_CONCAVE, (1.0,), verts=quad(0.0, 3.0)[:, ::-1].copy().reshape(-1, 3))                         # normals +z, two-sided
+    sc.add_bodies(1, mode=MODE_STATIC, shape=wall)
+    x2 = IDENT12.copy()
+    x2[11] = 0.5
+    sc.add_bodies(1, mode=MODE_STATIC, shape=wall2, xf=x2)
+    w = d = 9
+    gx, gz = np.meshgrid(np.arange(w) - 4.0, np.arange(d) - 4.0, indexing="xy")
+    h = (0.3 * np.sin(gx * 0.8) * np.cos(gz * 0.6)).astype(np.float32)
+    verts = np.zeros((w * d, 3), np.float32)
+    verts[:, 0] = h.reshape(-1)
+    hm = sc.add_shape(SHAPE_HEIGHTMAP, (w, d, float(h.min()) - 0.1, float(h.max()) + 0.1), verts=verts)
+    xh = IDENT12.copy()
+    xh[9], xh[10] = 20.0, -6.0
+    sc.add_bodies(1, mode=MODE_STATIC, shape=hm, xf=xh)
+    ball = sc.add_shape(SHAPE_SPHERE, (0.1, 0, 0, 0))
+    cube = sc.add_shape(SHAPE_BOX, (0.08, 0.08, 0.08, 0))
+    rng = np.random.default_rng(6)
+    xf = np.tile(IDENT12, (n, 1))
+    xf[:, 9] = rng.uniform(-2.6, 2.6, n)
+    xf[:, 10] = rng.uniform(-2.5, 2.5, n)
+    xf[:, 11] = -rng.uniform(2.3, 7.7, n)
+    shape = np.where(np.arange(n) % 3 == 0, cube, ball).astype(np.uint32)
+    flags = np.where(np.arange(n) % 2 == 0, 3, 1).astype(np.uint32)
+    lin = np.zeros((n, 3), np.float32)
+    lin[:, 2] = 60.0
+    sc.add_bodies(n, shape=shape, xf=xf, flags=flags, linvel=lin, mass=0.2, gravity_scale=0.0)
+    m = 6
+    xd = np.tile(IDENT12, (m, 1))
+    xd[:, 9] = 20.0 + rng.uniform(-3.0, 3.0, m)
+    xd[:, 10] = rng.uniform(-3.5, 0.5, m)
+    xd[:, 11] = rng.uniform(-3.0, 3.0, m)
+    lin = np.zeros((m, 3), np.float32)
+    lin[:, 1] = -60.0
+    lin[:, 0] = rng.uniform(-4.0, 4.0, m)
+    sc.add_bodies(m, shape=np.where(np.arange(m) % 2 == 0, ball, cube).astype(np.uint32), xf=xd, flags=np.where(np.arange(m) % 3 != 2, 3, 1).astype(np.uint32),
+                  linvel=lin, mass=0.2, gravity_scale=0.0)
+    return sc
+
+
 PUSH_FLAG = 8   # scene flag bit3: the harness applies a force and a torque to the body before every step
 
 

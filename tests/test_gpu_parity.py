@@ -269,6 +269,30 @@ def test_continuous_collision_detection_matches_the_reference():
     assert np.max(np.abs(z - ref_z)) < 0.05, np.abs(z - ref_z).max()
 
 
+def test_continuous_collision_detection_against_meshes_matches_the_reference():
+    """_test_ccd casting at a ConcavePolygonShape3D (one-sided and two-sided faces) and at a HeightMapShape3D: the other
+    shape's intersect_segment is the mesh's tree walk / the height map's cell walk.  Step by step with the reference; the
+    bullets with the CCD flag stay on their side of the walls and above the height map, the others fly through."""
+    _need_oracle()
+    sc = scenes.mesh_bullets()
+    w = parity.teacher_forced(sc, 30, list(range(1, 29)))
+    assert w["state"] < STATE_TOL and w["contact"] < CONTACT_TOL and w["colliding"] > 0, w
+    _, dump = parity.run_oracle(sc, 30, dump_from=30, dump_every=1)
+    ps = parity.new_server(sc, dump)
+    for _ in range(30):
+        ps.step(sc.dt)
+    x = ps.bodies_read(server.FIELD_TRANSFORM)
+    ps.finish()
+    ref = dump[("bodies", 30)]
+    assert np.max(np.abs(x[:, 9:12] - ref[:, 9:12])) < 0.05, np.abs(x[:, 9:12] - ref[:, 9:12]).max()
+    ccd = (sc.bodies["flags"] & 2) != 0
+    side = np.arange(len(ccd)) >= 4
+    flat = side & (np.arange(len(ccd)) < 16)
+    assert np.all(x[ccd & flat, 11] < 1.0) and np.sum(x[~ccd & flat, 11] > 10.0) >= 3
+    down = np.arange(len(ccd)) >= 16
+    assert np.all(x[ccd & down, 10] > -7.0) and np.sum(x[~ccd & down, 10] < -9.0) >= 2
+
+
 def test_applied_forces_and_torques_match_the_reference():
     """a2, the force accumulators: body_apply_central_force / body_apply_torque before every step (BPC_FIELD_APPLIED_FORCE
     through the C ABI), consumed and cleared by the step."""

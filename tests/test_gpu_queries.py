@@ -56,6 +56,40 @@ def test_intersect_rays_convex_hulls():
     assert _compare(sc, _rays(4000, 6, 4.0, 8.0), 50, [1, 25, 49]) > 2000
 
 
+def test_intersect_rays_height_map():
+    """BradotHeightMapShape3D::intersect_segment (bradot_shape_3d.cpp:1950-2008; the cell walk of _intersect_grid_segment,
+    :1810-1948): rays over the height-map scene -- steep ones that stay inside one cell, long oblique ones that walk many
+    cells, rays from below (back faces: hit only inside one cell), rays along the lanes."""
+    parity_needed()
+    sc = scenes.heightmap_pile()
+    rays = _rays(4000, 43, 6.5, 4.0)
+    rng = np.random.default_rng(7)
+    rays[:1000, 1] = rng.uniform(1.0, 3.0, 1000)
+    rays[:1000, 3:6] = rays[:1000, 0:3] + np.array([0, -5.0, 0]) + rng.normal(size=(1000, 3)) * np.array([0.1, 0, 0.1])      # steep
+    rays[1000:1500, 1] = rng.uniform(-3.0, -1.0, 500)
+    rays[1000:1500, 3:6] = rays[1000:1500, 0:3] + np.array([0, 5.0, 0]) + rng.normal(size=(500, 3)) * np.array([0.3, 0, 0.3])  # from below
+    rays[1500:1700, 0] = np.round(rays[1500:1700, 0])                                                                       # starting on a lane
+    rays[1700:1900, 3] = rays[1700:1900, 0]                                                                                 # along z only
+    rays = rays.astype(np.float32)
+    _, dump = parity.run_oracle(sc, 3, dump_from=0, dump_every=1, rays=rays)
+    ps = parity.new_server(sc, dump)
+    parity.load_state(ps, dump, 1)
+    hit, body, pos, nrm = ps.intersect_rays(rays)
+    ref = dump[("rays", 1)]
+    rhit = ref[:, 0] > 0
+    same = hit == rhit
+    assert same.mean() > 0.998, int((~same).sum())
+    both = hit & rhit
+    agree = body[both] == ref[both, 1].astype(np.int64)
+    assert agree.mean() > 0.998, int((~agree).sum())
+    sel = np.nonzero(both)[0][agree]
+    close = (np.abs(pos[sel] - ref[sel, 2:5]).max(axis=1) < POS_TOL) & (np.abs(nrm[sel] - ref[sel, 5:8]).max(axis=1) < NRM_TOL)
+    assert close.mean() > 0.998, int((~close).sum())
+    on_map = body[sel] == 1
+    assert on_map.sum() > 1200 and (on_map & (sel < 1000)).sum() > 500
+    ps.finish()
+
+
 def test_intersect_rays_edge_cases():
     sc = scenes.spheres_container(3, 3, 3, half=1.75)
     ps = server.PhysicsServerCUDA(0)
