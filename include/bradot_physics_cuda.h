@@ -144,8 +144,8 @@ int bpc_shape_create_concave(bpc_context *ctx, const float *faces, int n_faces, 
                              const float *normals);
 /* HeightMapShape3D (P3D/bradot_shape_3d.cpp:2028-2078, 2159-2178): width x depth heights row by row (z major), one unit apart,
  * centred on the shape's origin, solid on both sides; static bodies only.  Collides in the step and answers intersect_shape,
- * collide_shape, rest_info, cast_motion and body_test_motion like a triangle mesh; rays pass through it (the reference's grid
- * walk for segments is not built). */
+ * collide_shape, rest_info, cast_motion and body_test_motion like a triangle mesh; intersect_ray and the casts of CCD walk
+ * the cells under the segment in crossing order (BradotHeightMapShape3D::intersect_segment, :1950-2008). */
 int bpc_shape_create_heightmap(bpc_context *ctx, const float *heights, int width, int depth, float min_height, float max_height);
 
 /* ---- bodies */
