@@ -57,7 +57,7 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
     }
     ctx->except_keys.free_(); ctx->con_list.free_(); ctx->con_color.free_(); ctx->con_sorted.free_(); ctx->con_sorted_alt.free_();
     ctx->con_info.free_(); ctx->con_bin.free_(); ctx->con_sorted_color.free_(); ctx->joint_color.free_(); ctx->report_cap.free_(); ctx->report_ofs.free_(); ctx->report_count.free_(); ctx->reports.free_(); ctx->report_overflow.free_(); ctx->report_overflow_body.free_(); ctx->con_cls.free_(); ctx->bin_tab.free_(); ctx->bin_base.free_(); ctx->body_best.free_(); ctx->body_colmask.free_(); ctx->color_start.free_(); ctx->scontacts.free_();
-    ctx->forced_order.free_(); ctx->forced_level_start.free_(); ctx->forced_keys.free_(); ctx->d_joints.free_(); ctx->d_jext.free_();
+    ctx->forced_order.free_(); ctx->forced_level_start.free_(); ctx->forced_keys.free_(); ctx->d_joints.free_(); ctx->d_jext.free_(); ctx->d_shape_bias.free_();
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     delete ctx;
 }
@@ -202,6 +202,16 @@ extern "C" int bpc_reserve(bpc_context *ctx, int bodies, int pairs) {
 }
 
 // ---------------------------------------------------------------------------------------------- shapes
+extern "C" int bpc_shape_set_custom_bias(bpc_context *ctx, int shape, float bias) {
+    if (!ctx) return -1;
+    if (shape < 0 || (size_t)shape >= ctx->h_shapes.size()) return fail(ctx, "bpc_shape_set_custom_bias: invalid shape");
+    if (ctx->h_shape_bias.empty() && bias == 0.f) return 0;
+    ctx->h_shape_bias.resize(ctx->h_shapes.size(), 0.f);
+    ctx->h_shape_bias[shape] = bias;
+    ctx->shapes_dirty = true;
+    return 0;
+}
+
 extern "C" int bpc_shape_create(bpc_context *ctx, int type, const float p[4]) {
     if (!ctx) return -1;
     ShapeRec r;
@@ -498,6 +508,10 @@ int bpc_flush_tables(bpc_context *ctx) {
             upload(ctx, ctx->mplanes, ctx->h_mplanes) || upload(ctx, ctx->medges, ctx->h_medges) || upload(ctx, ctx->mfaces, ctx->h_mfaces) ||
             upload(ctx, ctx->mindex, ctx->h_mindex))
             return -1;
+        if (!ctx->h_shape_bias.empty()) {
+            ctx->h_shape_bias.resize(ctx->h_shapes.size(), 0.f);
+            if (upload(ctx, ctx->d_shape_bias, ctx->h_shape_bias)) return -1;
+        }
         ctx->shapes_dirty = false;
     }
     if (ctx->joints_dirty) {

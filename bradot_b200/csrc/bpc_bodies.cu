@@ -615,6 +615,7 @@ extern "C" int bpc_joints_create(bpc_context *ctx, const bpc_joint_desc *descs, 
     for (const JointRec &r : recs) {
         want_ext |= r.type == BPC_JOINT_SLIDER || r.type == BPC_JOINT_6DOF;
         ctx->have_g6dof |= r.type == BPC_JOINT_6DOF;
+        ctx->have_ext_joints |= r.type >= BPC_JOINT_CONE_TWIST;
     }
     if (want_ext) {
         ctx->h_jext.resize(ctx->h_joints.size() * JEXT_STRIDE, 0.f);

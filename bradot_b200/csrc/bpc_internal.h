@@ -237,6 +237,8 @@ struct bpc_context {
     std::vector<uint32_t> h_mindex; // per face: [count, idx...] packed; face_ofs indexes h_mfaces
     std::vector<uint2> h_mfaces;    // (index_ofs, count)
     std::vector<JointRec> h_joints;
+    std::vector<float> h_shape_bias; // shape_set_custom_solver_bias per shape; empty until one is set
+    DevBuf<float> d_shape_bias;
     std::vector<float> h_jext; // JEXT_STRIDE values per joint, present once a joint with a long parameter table exists
     DevBuf<float> d_jext;
     bool shapes_dirty = true, joints_dirty = true, spaces_dirty = true;
@@ -251,6 +253,7 @@ struct bpc_context {
     DevBuf<JointSetup> jsetup;
     DevBuf<G6Setup> jsetup6; // one per joint, present once a 6-DOF joint exists
     bool have_g6dof = false;
+    bool have_ext_joints = false; // a cone twist, slider or 6-DOF joint exists: the solve kernels that know them run
     DevBuf<uint32_t> a_range_cur; // same for the current pair list (vertex-centric island pass)
     DevBuf<uint32_t> a_range; // [2 * n_bodies]: begin / end of each body's run (as A) in the previous pair list
     DevBuf<uint32_t> io_slots; // body indices of a gather / scatter call

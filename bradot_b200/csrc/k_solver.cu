@@ -55,6 +55,8 @@ struct SvArgs {
     uint32_t *report_count;
     ReportRec *reports, *report_overflow;
     uint32_t *report_overflow_body;
+    const uint32_t *shape_id; // with shape_bias (null when no shape has a custom solver bias): the bias of a body's shape
+    const float *shape_bias;
     // continuous collision detection only
     const BodyXf *shape_xf;
     const float4 *shape_p;
@@ -314,7 +316,11 @@ __device__ inline void pre_solve_pair(const SvArgs &a, const ShBodies &sb, uint3
     M3 bA(f4v(xa.r0), f4v(xa.r1), f4v(xa.r2)), bB(f4v(xb.r0), f4v(xb.r1), f4v(xb.r2));
     V3 offset_B = f4v(xb.o) - f4v(xa.o);
     const float max_pen = space.max_penetration;
-    const float bias = 0.8f; // literal in the reference; SPACE_PARAM_CONTACT_DEFAULT_BIAS is not consulted (bradot_body_pair_3d.cpp:344)
+    float bias = 0.8f; // literal in the reference; SPACE_PARAM_CONTACT_DEFAULT_BIAS is not consulted (bradot_body_pair_3d.cpp:344)
+    if (a.shape_bias) { // shape_set_custom_solver_bias (:349-357)
+        float ba = a.shape_bias[a.shape_id[ia]], bb = a.shape_bias[a.shape_id[ib]];
+        if (ba != 0.f || bb != 0.f) bias = (ba == 0.f) ? bb : ((bb == 0.f) ? ba : (bb + ba) * 0.5f);
+    }
     float friction = fabsf(fminf(fA, fB));
     float cb = boA + boB;
     cb = cb < 0.f ? 0.f : (cb > 1.f ? 1.f : cb);
@@ -879,10 +885,11 @@ __device__ __forceinline__ void load_joint_static(const SvArgs &a, uint32_t i, B
     b.inv_mass = m.m.x;
 }
 
-template <bool SH>
-__device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t s, int it, uint32_t round) {
-    uint4 inf = a.info[s];
-    if (it >= (int)(inf.z >> 24) || round > ((inf.z >> 20) & 15u)) return;
+// EXT = false: pin and hinge, inlined in the sweep loops; EXT = true: the cone twist, the slider and the 6-DOF joint, which
+// solve_joint reaches through one out-of-line call (their code inlined beside the contact solver cost the joint-free
+// scenes a quarter of their solve time: measured, C5 5.7 -> 7.3 ms)
+template <bool SH, bool EXT>
+__device__ __forceinline__ void solve_joint_body(const SvArgs &a, const ShBodies &sb, uint32_t s, uint4 inf) {
     const JointSetup js = a.jsetup[inf.w];
     uint32_t flags = __float_as_uint(js.pa.w);
     if (!(flags & 4u)) return;
@@ -899,7 +906,7 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
     const float4 rows[3] = { js.n0, js.n1, js.n2 };
     uint32_t type = (inf.z >> 16) & 15u;
     const float tau = js.prm.x;
-    if (type == 0) { // pin: the relative velocity is re-read for every axis
+    if (!EXT && type == 0) { // pin: the relative velocity is re-read for every axis
         const float damping = js.prm.y, clamp = js.prm.z;
         for (int i = 0; i < 3; i++) {
             V3 normal = f4v(rows[i]);
@@ -918,7 +925,7 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
             if (dynA) apply_impulse(A, iv, pA);
             if (dynB) apply_impulse(B, -iv, pB);
         }
-    } else if (type == 2) { // cone twist (joints/bradot_cone_twist_joint_3d.cpp:205-279)
+    } else if (EXT && type == 2) { // cone twist (joints/bradot_cone_twist_joint_3d.cpp:205-279)
         V3 vel1 = A.lin + cross(A.ang, pA - A.com);
         V3 vel2 = B.lin + cross(B.ang, pB - B.com);
         V3 vel = vel1 - vel2;
@@ -959,7 +966,7 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
             if (dynA) A.ang += xform(A.iinv, impulse);
             if (dynB) B.ang += xform(B.iinv, -impulse);
         }
-    } else if (type == 4) { // generic 6-DOF (joints/bradot_generic_6dof_joint_3d.cpp:372-417; solveLinearAxis :159-218, solveAngularLimits :86-155)
+    } else if (EXT && type == 4) { // generic 6-DOF (joints/bradot_generic_6dof_joint_3d.cpp:372-417; solveLinearAxis :159-218, solveAngularLimits :86-155)
         G6Setup &g = a.jsetup6[inf.w];
         const uint32_t lin_bits = __float_as_uint(g.lin_acc.w), ang_bits = __float_as_uint(g.ang_c.w);
         float lacc[3] = { g.lin_acc.x, g.lin_acc.y, g.lin_acc.z };
@@ -1011,7 +1018,7 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
             g.ang_acc.y = aacc[1];
             g.ang_acc.z = aacc[2];
         }
-    } else if (type == 3) { // slider (joints/bradot_slider_joint_3d.cpp:141-275; its motors cannot be switched on through the server)
+    } else if (EXT && type == 3) { // slider (joints/bradot_slider_joint_3d.cpp:141-275; its motors cannot be switched on through the server)
         V3 vel = (A.lin + cross(A.ang, pA - A.com)) - (B.lin + cross(B.ang, pB - B.com));
         const float depth[3] = { js.dpos.x, js.dpos.y, js.dpos.z };
         for (int i = 0; i < 3; i++) {
@@ -1054,7 +1061,7 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
         V3 impulse = axisA * impulseMag;
         if (dynA) A.ang += xform(A.iinv, impulse);
         if (dynB) B.ang += xform(B.iinv, -impulse);
-    } else { // hinge: one velocity sample for the three linear rows
+    } else if (!EXT) { // hinge: one velocity sample for the three linear rows
         V3 vel1 = A.lin + cross(A.ang, pA - A.com);
         V3 vel2 = B.lin + cross(B.ang, pB - B.com);
         V3 vel = vel1 - vel2;
@@ -1120,6 +1127,21 @@ __device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t
     if (dynB) store_body<SH, 2>(a, sb, inf.y, B);
 }
 
+template <bool SH>
+__device__ __noinline__ void solve_joint_ext(const SvArgs *a, const ShBodies *sb, uint32_t s, uint4 inf) {
+    solve_joint_body<SH, true>(*a, *sb, s, inf);
+}
+
+// EXTJ: the scene holds a joint of those types (the kernels exist in both forms; a scene without one runs code that has no
+// trace of them -- even the never-taken call cost 0.2 ms of C5's 6 ms solve)
+template <bool SH, bool EXTJ>
+__device__ inline void solve_joint(const SvArgs &a, const ShBodies &sb, uint32_t s, int it, uint32_t round) {
+    uint4 inf = a.info[s];
+    if (it >= (int)(inf.z >> 24) || round > ((inf.z >> 20) & 15u)) return;
+    if (EXTJ && ((inf.z >> 16) & 15u) >= 2u) solve_joint_ext<SH>(&a, &sb, s, inf);
+    else solve_joint_body<SH, false>(a, sb, s, inf);
+}
+
 __device__ inline void pre_solve_joint(const SvArgs &a, uint32_t s, uint32_t j) {
     const JointRec &jr = a.joints[j];
     uint32_t iters = (uint32_t)a.spaces[a.meta[jr.a].w].iterations;
@@ -1174,6 +1196,7 @@ __global__ void __launch_bounds__(SV_THREADS) k_presolve(SvArgs a) {
 #ifndef SV_MIN_BLOCKS
 #define SV_MIN_BLOCKS 3
 #endif
+template <bool EXTJ>
 __global__ void __launch_bounds__(SV_THREADS, SV_MIN_BLOCKS) k_sweeps(SvArgs a) {
     cg::grid_group grid = cg::this_grid();
     uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
@@ -1190,14 +1213,14 @@ __global__ void __launch_bounds__(SV_THREADS, SV_MIN_BLOCKS) k_sweeps(SvArgs a) 
                         for (uint32_t s = lo; s < hi; s++) {
                             uint32_t id = a.sched[s];
                             if (id < a.n_pairs) solve_pair<false>(a, none, s, it, round);
-                            else if (id != 0xffffffffu) solve_joint<false>(a, none, s, it, round);
+                            else if (id != 0xffffffffu) solve_joint<false, EXTJ>(a, none, s, it, round);
                         }
                     }
                 } else {
                     for (uint32_t s = lo + tid; s < hi; s += nth) {
                         uint32_t id = a.sched[s];
                         if (id < a.n_pairs) solve_pair<false>(a, none, s, it, round);
-                        else if (id != 0xffffffffu) solve_joint<false>(a, none, s, it, round);
+                        else if (id != 0xffffffffu) solve_joint<false, EXTJ>(a, none, s, it, round);
                     }
                 }
                 grid.sync();
@@ -1224,6 +1247,7 @@ __global__ void __launch_bounds__(SV_THREADS, SV_MIN_BLOCKS) k_sweeps(SvArgs a) 
 #else
 #define SB_SYNC() __syncthreads()
 #endif
+template <bool EXTJ>
 __global__ void __launch_bounds__(SB_THREADS) k_solve_bins(SvArgs a) {
     extern __shared__ float4 sb_mem[];
     const uint32_t bin = blockIdx.x;
@@ -1307,14 +1331,14 @@ __global__ void __launch_bounds__(SB_THREADS) k_solve_bins(SvArgs a) {
                         for (uint32_t q = lo; q < hi; q++) {
                             uint32_t s = seg_lo + order[q];
                             if (a.sched[s] < a.n_pairs) solve_pair<true>(a, sb, s, it, round);
-                            else solve_joint<true>(a, sb, s, it, round);
+                            else solve_joint<true, EXTJ>(a, sb, s, it, round);
                         }
                     }
                 } else {
                     for (uint32_t q = lo + lane; q < hi; q += SB_THREADS) {
                         uint32_t s = seg_lo + order[q];
                         if (a.sched[s] < a.n_pairs) solve_pair<true>(a, sb, s, it, round);
-                        else solve_joint<true>(a, sb, s, it, round);
+                        else solve_joint<true, EXTJ>(a, sb, s, it, round);
                     }
                 }
                 SB_SYNC();
@@ -1425,6 +1449,8 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     a.report_overflow_body = ctx->report_overflow_body.p;
     a.shape_xf = ctx->shape_xf.p;
     a.shape_p = ctx->shape_p.p;
+    a.shape_id = ctx->shape_id.p;
+    a.shape_bias = ctx->h_shape_bias.empty() ? nullptr : ctx->d_shape_bias.p;
     a.medges = ctx->medges.p;
     a.pools.meshes = ctx->meshes.p;
     a.pools.mverts = ctx->mverts.p;
@@ -1439,7 +1465,8 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     a.max_priority = nj ? ctx->max_priority : 1u;
     a.counters = ctx->counters.p;
     void *args[] = { &a };
-    void *kernels[2] = { ctx->h_ccd_ids.empty() ? (void *)k_presolve<false> : (void *)k_presolve<true>, (void *)k_sweeps };
+    void *kernels[2] = { ctx->h_ccd_ids.empty() ? (void *)k_presolve<false> : (void *)k_presolve<true>,
+                         ctx->have_ext_joints ? (void *)k_sweeps<true> : (void *)k_sweeps<false> };
     for (int k = 0; k < 2; k++) {
         int per_sm = 0;
         BPC_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)kernels[k], SV_THREADS, 0));
@@ -1451,14 +1478,16 @@ int bpc_launch_solver(bpc_context *ctx, float dt) {
     ctx->launches += 2;
     if (!ctx->n_forced_levels && ctx->n_bins) {
         static bool attr_set = false;
+        auto bins_kernel = ctx->have_ext_joints ? k_solve_bins<true> : k_solve_bins<false>;
         size_t smem = (size_t)BIN_MAX_BODIES * SB_STRIDE * sizeof(float) + BIN_MAX_BODIES + BIN_MAX_CONS * sizeof(uint16_t) +
                       (BIN_KEYS_SV + 1 + BIN_COLS_SV + 1) * sizeof(uint32_t);
         smem = (smem + 15) & ~(size_t)15;
         if (!attr_set) {
-            BPC_CHECK(cudaFuncSetAttribute(k_solve_bins, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            BPC_CHECK(cudaFuncSetAttribute(k_solve_bins<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            BPC_CHECK(cudaFuncSetAttribute(k_solve_bins<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             attr_set = true;
         }
-        k_solve_bins<<<ctx->n_bins, SB_THREADS, smem, st>>>(a);
+        bins_kernel<<<ctx->n_bins, SB_THREADS, smem, st>>>(a);
         BPC_CHECK(cudaGetLastError());
         ctx->launches += 1;
     }

@@ -18,7 +18,7 @@ SHAPE_PLANE, SHAPE_RAY, SHAPE_SPHERE, SHAPE_BOX, SHAPE_CAPSULE, SHAPE_CYLINDER, 
 MODE_STATIC, MODE_KINEMATIC, MODE_RIGID, MODE_RIGID_LINEAR = range(4)
 JOINT_PIN, JOINT_HINGE, JOINT_CONE_TWIST, JOINT_SLIDER, JOINT_6DOF = 0, 1, 2, 3, 4
 
-SHAPE_DT = np.dtype([("type", "<u4"), ("p", "<f4", 4), ("vert_ofs", "<u4"), ("vert_cnt", "<u4"), ("pad", "<u4")])
+SHAPE_DT = np.dtype([("type", "<u4"), ("p", "<f4", 4), ("vert_ofs", "<u4"), ("vert_cnt", "<u4"), ("custom_bias", "<f4")])   # custom_bias: shape_set_custom_solver_bias, 0 = none
 BODY_DT = np.dtype([
     ("space", "<u4"), ("mode", "<u4"), ("shape", "<u4"), ("flags", "<u4"),
     ("xf", "<f4", 12), ("shape_xf", "<f4", 12), ("linvel", "<f4", 3), ("angvel", "<f4", 3),

@@ -42,7 +42,7 @@ EXPORTS = [
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
     "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
     "bpc_bodies_set_state", "bpc_bodies_read_slots", "bpc_bodies_write_slots", "bpc_bodies_read_state", "bpc_reserve",
-    "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_joint_params_write", "bpc_joint_params_read", "bpc_test_segment_math", "bpc_bodies_set_exception",
+    "bpc_shape_set_custom_bias", "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_joint_params_write", "bpc_joint_params_read", "bpc_test_segment_math", "bpc_bodies_set_exception",
     "bpc_bodies_set_max_contacts_reported", "bpc_body_read_contacts", "bpc_contacts_capacity", "bpc_contacts_read",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
     "bpc_space_set_query_exclude", "bpc_space_rest_infos", "bpc_space_cast_motions",
@@ -98,6 +98,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_joints_create.argtypes = [vp, vp, ci]
     lib.bpc_joints_write.argtypes = [vp, ci, ci, vp]
     lib.bpc_joints_destroy.argtypes = [vp, ci, ci]
+    lib.bpc_shape_set_custom_bias.argtypes = [vp, ci, ctypes.c_float]
     lib.bpc_joint_params_write.argtypes = [vp, ci, ci, ci, vp]
     lib.bpc_joint_params_read.argtypes = [vp, ci, ci, ci, vp]
     lib.bpc_joint_count.argtypes = [vp]
@@ -343,6 +344,10 @@ class PhysicsServerCUDA:
         rec = np.ascontiguousarray(records, scenes.JOINT_DT)
         self._check(self.lib.bpc_joints_write(self.ctx, int(first), len(rec), _ptr(rec)))
 
+    def shape_set_custom_bias(self, shape, bias):
+        """shape_set_custom_solver_bias: the contact bias of pairs with this shape (0 = the default 0.8)."""
+        self._check(self.lib.bpc_shape_set_custom_bias(self.ctx, int(shape), float(bias)))
+
     def joint_params_write(self, joint, first, values):
         """slider_joint_set_param: values of the joint's long parameter table from parameter `first` on."""
         v = np.ascontiguousarray(values, np.float32).reshape(-1)
@@ -532,6 +537,9 @@ class PhysicsServerCUDA:
                 self.convex_polygon_shape_create(mesh)
             else:
                 self.shape_create(int(s["type"]), s["p"])
+        for i, s in enumerate(sc.shapes):
+            if s["custom_bias"] != 0:
+                self.shape_set_custom_bias(i, float(s["custom_bias"]))
         bodies = sc.bodies
         kin = bodies["mode"] == scenes.MODE_KINEMATIC
         if kin.any():   # in a scene file a kinematic body's velocities are its motion script (oracle/ref_harness.cpp), not body state

@@ -165,7 +165,57 @@ int BradotPhysicsServerCUDA::_shape_handle(Shape *p_shape) {
 			ERR_FAIL_V_MSG(-1, "BradotPhysicsCUDA: unsupported shape type.");
 	}
 	ERR_FAIL_COND_V_MSG(p_shape->handle < 0, -1, bpc_last_error(ctx));
+	if (p_shape->custom_bias != 0.0) {
+		bpc_shape_set_custom_bias(ctx, p_shape->handle, (float)p_shape->custom_bias);
+	}
 	return p_shape->handle;
+}
+
+// the reference has no custom shapes either (bradot_physics_server_3d.cpp:102-104)
+RID BradotPhysicsServerCUDA::custom_shape_create() {
+	ERR_FAIL_V(RID());
+}
+
+// shape_set_custom_solver_bias (bradot_physics_server_3d.cpp:110-116): used by the pair setup in place of 0.8
+void BradotPhysicsServerCUDA::shape_set_custom_solver_bias(RID p_shape, real_t p_bias) {
+	Shape *shape = shape_owner.get_or_null(p_shape);
+	ERR_FAIL_NULL(shape);
+	shape->custom_bias = p_bias;
+	if (shape->handle >= 0) {
+		ERR_FAIL_COND_MSG(bpc_shape_set_custom_bias(ctx, shape->handle, (float)p_bias) < 0, bpc_last_error(ctx));
+	}
+}
+
+real_t BradotPhysicsServerCUDA::shape_get_custom_solver_bias(RID p_shape) const {
+	const Shape *shape = shape_owner.get_or_null(p_shape);
+	ERR_FAIL_NULL_V(shape, 0);
+	return shape->custom_bias;
+}
+
+// the following are accepted and ignored by the reference as well (bradot_physics_server_3d.cpp:131-136, 648-657, 859-868)
+void BradotPhysicsServerCUDA::shape_set_margin(RID p_shape, real_t p_margin) {
+}
+
+real_t BradotPhysicsServerCUDA::shape_get_margin(RID p_shape) const {
+	return 0.0;
+}
+
+void BradotPhysicsServerCUDA::body_set_user_flags(RID p_body, uint32_t p_flags) {
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body));
+}
+
+uint32_t BradotPhysicsServerCUDA::body_get_user_flags(RID p_body) const {
+	ERR_FAIL_NULL_V(body_owner.get_or_null(p_body), 0);
+	return 0;
+}
+
+void BradotPhysicsServerCUDA::body_set_contacts_reported_depth_threshold(RID p_body, real_t p_threshold) {
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body));
+}
+
+real_t BradotPhysicsServerCUDA::body_get_contacts_reported_depth_threshold(RID p_body) const {
+	ERR_FAIL_NULL_V(body_owner.get_or_null(p_body), 0);
+	return 0;
 }
 
 /* SPACES */
@@ -1496,6 +1546,37 @@ void BradotPhysicsServerCUDA::joint_make_hinge(RID p_joint, RID p_body_A, const 
 	joint->fb = p_hinge_B;
 	joint->pending = true;
 	pending_joints.push_back(joint);
+}
+
+// joint_make_hinge_simple (bradot_physics_server_3d.cpp:1320-1342): pivots and axes instead of frames; the frames are built as
+// the reference's second hinge constructor builds them (joints/bradot_hinge_joint_3d.cpp:69-108) from body A's transform
+// at this moment.  (That constructor stores -axis_B in frame B; joint_make_hinge's flips the z column of the frame it is
+// given, so +axis_B is handed over here.)
+void BradotPhysicsServerCUDA::joint_make_hinge_simple(RID p_joint, RID p_body_A, const Vector3 &p_pivot_A, const Vector3 &p_axis_A, RID p_body_B, const Vector3 &p_pivot_B, const Vector3 &p_axis_B) {
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body_A));
+	ERR_FAIL_NULL(body_owner.get_or_null(p_body_B));
+	const Basis ba = Transform3D(body_get_state(p_body_A, BODY_STATE_TRANSFORM)).basis;
+	Vector3 a1 = ba.get_column(0), a2;
+	real_t projection = p_axis_A.dot(a1);
+	if (projection >= 1.0f - CMP_EPSILON) {
+		a1 = -ba.get_column(2);
+		a2 = ba.get_column(1);
+	} else if (projection <= -1.0f + CMP_EPSILON) {
+		a1 = ba.get_column(2);
+		a2 = ba.get_column(1);
+	} else {
+		a2 = p_axis_A.cross(a1);
+		a1 = a2.cross(p_axis_A);
+	}
+	Transform3D fa, fb;
+	fa.origin = p_pivot_A;
+	fa.basis = Basis(a1.x, a2.x, p_axis_A.x, a1.y, a2.y, p_axis_A.y, a1.z, a2.z, p_axis_A.z);
+	Quaternion arc(p_axis_A, p_axis_B);
+	Vector3 b1 = arc.xform(a1);
+	Vector3 b2 = p_axis_B.cross(b1);
+	fb.origin = p_pivot_B;
+	fb.basis = Basis(b1.x, b2.x, p_axis_B.x, b1.y, b2.y, p_axis_B.y, b1.z, b2.z, p_axis_B.z);
+	joint_make_hinge(p_joint, p_body_A, fa, p_body_B, fb);
 }
 
 void BradotPhysicsServerCUDA::joint_disable_collisions_between_bodies(RID p_joint, bool p_disable) {

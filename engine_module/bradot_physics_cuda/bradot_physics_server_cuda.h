@@ -110,6 +110,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	struct Shape {
 		ShapeType type = SHAPE_SPHERE;
 		Variant data;
+		real_t custom_bias = 0.0;
 		int handle = -1; // bpc shape index, created lazily once the data is known
 	};
 	struct Space {
@@ -267,7 +268,17 @@ public:
 	virtual RID convex_polygon_shape_create() override;
 	virtual RID concave_polygon_shape_create() override;
 	virtual RID heightmap_shape_create() override;
+	virtual RID custom_shape_create() override;
 	virtual void shape_set_data(RID p_shape, const Variant &p_data) override;
+	virtual void shape_set_custom_solver_bias(RID p_shape, real_t p_bias) override;
+	virtual real_t shape_get_custom_solver_bias(RID p_shape) const override;
+	virtual void shape_set_margin(RID p_shape, real_t p_margin) override;
+	virtual real_t shape_get_margin(RID p_shape) const override;
+	virtual void body_set_user_flags(RID p_body, uint32_t p_flags) override;
+	virtual uint32_t body_get_user_flags(RID p_body) const override;
+	virtual void body_set_contacts_reported_depth_threshold(RID p_body, real_t p_threshold) override;
+	virtual real_t body_get_contacts_reported_depth_threshold(RID p_body) const override;
+	virtual void joint_make_hinge_simple(RID p_joint, RID p_body_A, const Vector3 &p_pivot_A, const Vector3 &p_axis_A, RID p_body_B, const Vector3 &p_pivot_B, const Vector3 &p_axis_B) override;
 	virtual ShapeType shape_get_type(RID p_shape) const override;
 	virtual Variant shape_get_data(RID p_shape) const override;
 	// spaces

@@ -36,7 +36,7 @@ public:
 #pragma pack(push, 1)
 struct ScnHeader { char magic[4]; uint32_t version, n_spaces, n_shapes, n_bodies, n_joints, n_verts; float dt; uint32_t iterations, iter_step, n_areas, n_joint_ext, reserved[4]; };
 struct ScnJointExt { uint32_t joint, first, count, pad; float values[28]; };
-struct ScnShape { uint32_t type; float p[4]; uint32_t vert_ofs, vert_cnt, pad; };
+struct ScnShape { uint32_t type; float p[4]; uint32_t vert_ofs, vert_cnt; float custom_bias; };
 struct ScnBody { uint32_t space, mode, shape, flags; float xf[12], shape_xf[12], linvel[3], angvel[3], mass, friction, bounce, gravity_scale, lin_damp, ang_damp; uint32_t layer, mask; };
 struct ScnJoint { uint32_t type, body_a, body_b, flags; float fa[12], fb[12], params[8]; uint32_t priority, pad[3]; };
 struct Event { int32_t step, body, kind; float v[12]; }; // kinds 6 / 7 address an area: area_set_transform / free
@@ -217,6 +217,9 @@ int main(int argc, char **argv) {
 			default:
 				fprintf(stderr, "unsupported shape\n");
 				return 2;
+		}
+		if (s.custom_bias != 0.0f) {
+			ps->shape_set_custom_solver_bias(sh, s.custom_bias);
 		}
 		shape_r.push_back(sh);
 	}

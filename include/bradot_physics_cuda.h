@@ -127,6 +127,9 @@ int bpc_space_destroy(bpc_context *ctx, int space);
 
 /* ---- shapes: shape_create + shape_set_data (P3D/bradot_physics_server_3d.cpp:50-142; P3D/bradot_shape_3d.cpp _setup) */
 int bpc_shape_create(bpc_context *ctx, int type, const float params[4]);
+/* shape_set_custom_solver_bias (P3D/bradot_physics_server_3d.cpp:110-116): a shape's own contact bias; a pair uses it in place
+ * of 0.8 -- the one that is set, or the mean of both (BradotBodyPair3D::setup, P3D/bradot_body_pair_3d.cpp:344-357).  0 = none. */
+int bpc_shape_set_custom_bias(bpc_context *ctx, int shape, float bias);
 /* Convex hull in the layout of Geometry3D::MeshData (core/math/geometry_3d.h): the engine-side
  * module runs ConvexHullComputer (host, set-up time only, P3D/bradot_shape_3d.cpp:1099) and hands
  * the result over.  faces: per face (first index, index count) into `indices`; edges: per edge

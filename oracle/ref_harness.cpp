@@ -85,7 +85,7 @@ struct ScnShape {
 	uint32_t type; // PhysicsServer3D::ShapeType
 	float p[4]; // plane: n.xyz,d | sphere: r | box: half extents | capsule: radius,height
 	uint32_t vert_ofs, vert_cnt; // convex
-	uint32_t pad;
+	float custom_bias; // shape_set_custom_solver_bias, 0 = none
 };
 struct ScnBody {
 	// flags bit0 can_sleep, bit1 ccd, bit2 start asleep, bit3 pushed every step (see push_bodies),
@@ -970,6 +970,9 @@ int main(int argc, char **argv) {
 			default:
 				fprintf(stderr, "unsupported shape type %u\n", s.type);
 				return 2;
+		}
+		if (s.custom_bias != 0.0f) {
+			ps->shape_set_custom_solver_bias(sh, s.custom_bias);
 		}
 		w.shapes.push_back(sh);
 	}

@@ -423,6 +423,30 @@ def test_height_maps_match_the_reference():
     assert w["contact"] < CONTACT_TOL and w["state"] < 1e-4, w
 
 
+def test_shape_custom_solver_bias_matches_the_reference():
+    """shape_set_custom_solver_bias (BradotBodyPair3D::setup, bradot_body_pair_3d.cpp:344-357): a pair takes the bias of the shape
+    that has one, or the mean of both, in place of 0.8.  A settling mixed pile where the spheres, the boxes and the floor
+    plane carry their own biases: teacher-forced, contacts 1e-5, state 1e-4; and the biases matter."""
+    _need_oracle()
+    sc = scenes.mixed_pile(4, half=3.0)
+    types = sc.shapes["type"]
+    sc.shapes["custom_bias"][types == scenes.SHAPE_SPHERE] = 0.3
+    sc.shapes["custom_bias"][types == scenes.SHAPE_BOX] = 0.55
+    sc.shapes["custom_bias"][np.nonzero(types == scenes.SHAPE_PLANE)[0][0]] = 0.2
+    assert (sc.shapes["custom_bias"] != 0).sum() >= 3 and (sc.shapes["custom_bias"] == 0).sum() >= 2
+    _, dump = parity.run_oracle(sc, 90)
+    w = parity.teacher_forced(sc, 90, [1, 30, 45, 60, 75, 88], dump=dump)
+    assert w["state"] < STATE_TOL and w["contact"] < CONTACT_TOL and w["contacts"] > 100, w
+    plain = scenes.mixed_pile(4, half=3.0)
+    ps = parity.new_server(plain, dump)
+    parity.load_state(ps, dump, 60)
+    ps.set_solve_order(parity.solve_order(dump, 61))
+    ps.step(sc.dt)
+    st = ps.bodies_read_state()
+    assert parity.rel_err(st[:, 0:12], dump[("bodies", 61)][:, 0:12], 1.0) > 1e-4
+    ps.finish()
+
+
 def test_slider_joints_match_the_reference():
     """SliderJoint3D (joints/bradot_slider_joint_3d.cpp:74-337): rigs of two boxes on slider joints in turned frames, default and
     own parameters (22 per joint through bpc_joint_params_write), linear and angular limits hit; teacher-forced with the
