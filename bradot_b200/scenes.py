@@ -627,6 +627,41 @@ def hanging_chains(n_chains=12, chain_len=5, seed=5, cone_twist=False):
     return sc
 
 
+JOINT_HINGE_SIMPLE = 16   # scene flag (harness / engine demo): make the hinge with joint_make_hinge_simple from the frames' origins and z axes
+
+
+def simple_hinges(n=12, seed=17):
+    """joint_make_hinge_simple: boxes hanging from static anchors by hinges given as pivots and axes (the z columns of the
+    scene's frames; the other columns are ignored).  The bodies start turned, the two axes differ, every second hinge has a
+    limit -- all of which enter the frames the reference builds from body A's transform at that moment."""
+    sc = Scene(name="simple_hinges_%d" % n)
+    anchor = sc.add_shape(SHAPE_BOX, (0.1, 0.1, 0.1))
+    link = sc.add_shape(SHAPE_BOX, (0.3, 0.12, 0.2))
+    rng = np.random.default_rng(seed)
+    for r in range(n):
+        xa = IDENT12.copy()
+        th = 0.3 * (r % 4)
+        xa[0], xa[2], xa[6], xa[8] = np.cos(th), np.sin(th), -np.sin(th), np.cos(th)      # anchors turned about y
+        xa[9], xa[10] = r * 6.0, 10.0
+        a = sc.add_bodies(1, mode=MODE_STATIC, shape=anchor, xf=xa, layer=0, mask=0)
+        xb = IDENT12.copy()
+        xb[9], xb[10] = r * 6.0 + 0.5, 9.7
+        b = sc.add_bodies(1, shape=link, xf=xb, mass=0.8, layer=0, mask=0, linvel=rng.uniform(-1, 1, 3).astype(np.float32),
+                          angvel=rng.uniform(-2, 2, 3).astype(np.float32), flags=0)
+        ax_a = np.array([0.2 * (r % 3), 0.1, 1.0]) if r % 5 else np.array([1.0, 0.0, 0.0])     # r % 5 == 0: along the anchor's x (the special case)
+        ax_b = np.array([0.1, 0.15 * (r % 2), 1.0])
+        ax_a, ax_b = ax_a / np.linalg.norm(ax_a), ax_b / np.linalg.norm(ax_b)
+        fa, fb = IDENT12.copy(), IDENT12.copy()
+        fa[[2, 5, 8]], fb[[2, 5, 8]] = ax_a, ax_b
+        fa[9:12], fb[9:12] = (0.2, -0.1, 0.0), (-0.3, 0.2, 0.0)
+        flags, prm = JOINT_NO_COLLIDE | JOINT_HINGE_SIMPLE, HINGE_DEFAULTS.copy()
+        if r % 2:
+            flags |= JOINT_USE_LIMIT | JOINT_HAS_PARAMS
+            prm[1], prm[2] = 0.4, -0.3
+        sc.add_joints(1, type=JOINT_HINGE, body_a=a, body_b=b, flags=flags, fa=fa, fb=fb, params=prm)
+    return sc
+
+
 def slider_rigs(n_rigs=18, seed=11):
     """Slider joints: rig r is a static anchor, a box hanging from it by a slider joint and a second box on the first by
     another one; no collisions (joint-only islands, as in hanging_chains).  The joint frames are turned so that the slider

@@ -313,7 +313,12 @@ int main(int argc, char **argv) {
 				}
 			}
 		} else {
-			ps->joint_make_hinge(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
+			if (j.flags & 16) { // joint_make_hinge_simple: pivots = the frame origins, axes = the z columns of the frames
+				ps->joint_make_hinge_simple(jr, body_r[j.body_a], Vector3(j.fa[9], j.fa[10], j.fa[11]), Vector3(j.fa[2], j.fa[5], j.fa[8]), body_r[j.body_b],
+						Vector3(j.fb[9], j.fb[10], j.fb[11]), Vector3(j.fb[2], j.fb[5], j.fb[8]));
+			} else {
+				ps->joint_make_hinge(jr, body_r[j.body_a], xf_from(j.fa), body_r[j.body_b], xf_from(j.fb));
+			}
 			if (j.flags & 8) {
 				for (int k = 0; k < (int)PhysicsServer3D::HINGE_JOINT_MAX; k++) {
 					ps->hinge_joint_set_param(jr, (PhysicsServer3D::HingeJointParam)k, j.params[k]);

@@ -1041,6 +1041,9 @@ int main(int argc, char **argv) {
 			ps->joint_make_slider(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		} else if (j.type == 4) {
 			ps->joint_make_generic_6dof(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
+		} else if (j.flags & 16) { // joint_make_hinge_simple: pivots = the frame origins, axes = the z columns of the frames
+			ps->joint_make_hinge_simple(jr, w.bodies[j.body_a], Vector3(j.fa[9], j.fa[10], j.fa[11]), Vector3(j.fa[2], j.fa[5], j.fa[8]), w.bodies[j.body_b],
+					Vector3(j.fb[9], j.fb[10], j.fb[11]), Vector3(j.fb[2], j.fb[5], j.fb[8]));
 		} else {
 			ps->joint_make_hinge(jr, w.bodies[j.body_a], xf_from(j.fa), w.bodies[j.body_b], xf_from(j.fb));
 		}

@@ -115,6 +115,26 @@ def test_engine_module_forces_and_ccd_match_direct_c_abi(tmp_path, name):
         assert np.all(direct[ccd, 2] < 3.0)        # stopped by the wall / the plates
 
 
+def test_engine_module_simple_hinges_match_the_reference(tmp_path):
+    """joint_make_hinge_simple through the module (the frames built from pivots, axes and body A's transform, as
+    joints/bradot_hinge_joint_3d.cpp:69-108 does) against the reference making the same hinges: free-running, positions to 2 mm."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    if not parity.have_oracle():
+        pytest.skip("oracle/_ref/oracle_step not built")
+    sc = scenes.simple_hinges()
+    steps = 50
+    path = str(tmp_path / "scene.bscn")
+    sc.write(path)
+    r = subprocess.run([DEMO, path, str(steps)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    engine = np.array(json.loads(r.stdout.strip().splitlines()[-1])["origins"], np.float32)
+    _, dump = parity.run_oracle(sc, steps, dump_steps=[steps])
+    ref = dump[("bodies", steps)][:, 9:12]
+    assert np.max(np.abs(engine - ref)) < 2e-3, float(np.abs(engine - ref).max())
+    assert np.max(np.abs(ref - sc.bodies["xf"][:, 9:12])) > 0.2        # they do swing
+
+
 def test_engine_module_callbacks_set_state_and_free_match_c_abi_and_reference(tmp_path):
     """A scene driven like a game drives it -- every body has a state-sync callback (what RigidBody3D registers), a script of
     body_set_state / free calls runs between the ticks -- through the RID API of the module, against (1) the same script on
