@@ -260,7 +260,7 @@ static int write_body_slots(bpc_context *ctx, const uint32_t *slots, const bpc_b
         mw[i].m = make_float4(inv_mass, d.friction, d.bounce, 0.f);
         uint32_t flags = (d.flags & 1u ? BF_CAN_SLEEP : 0u) | (d.flags & 4u ? 0u : BF_ACTIVE) | (d.flags & 2u ? BF_CCD : 0u) |
                          (d.flags & 16u ? BF_LIN_REPLACE : 0u) | (d.flags & 32u ? BF_ANG_REPLACE : 0u) | (d.flags & 64u ? BF_OMIT_FORCE : 0u) |
-                         (((d.flags >> 8) & 63u) << BF_LOCK_SHIFT);
+                         (d.flags & 128u ? BF_NOT_PICKABLE : 0u) | (((d.flags >> 8) & 63u) << BF_LOCK_SHIFT);
         if (keep_state) {
             uint32_t of = old_meta[i].x >> 8;
             flags = (flags & ~BF_ACTIVE) | (of & BF_ACTIVE);

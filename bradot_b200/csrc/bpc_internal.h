@@ -22,6 +22,7 @@ enum { MODE_STATIC = 0, MODE_KINEMATIC = 1, MODE_RIGID = 2, MODE_RIGID_LINEAR = 
 #define BF_FROZEN 16u      // the body's space is inactive (space_set_active(false)) or the body was destroyed: no stage touches it
 #define BF_LIN_REPLACE 32u // BODY_DAMP_MODE_REPLACE for the linear / angular damping (bradot_body_3d.cpp:586-606)
 #define BF_ANG_REPLACE 64u
+#define BF_NOT_PICKABLE 128u // body_set_ray_pickable(false)
 #define BF_LOCK_SHIFT 8 // 6 axis-lock bits, same order as PhysicsServer3D::BodyAxis
 #define BF_SHAPE_IDENT (1u << 14)  // the shape's local transform is the identity (no product needed)
 #define BF_ISLAND_AWAKE (1u << 15) // refreshed every step: the body's island holds an awake body

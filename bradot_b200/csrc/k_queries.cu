@@ -47,6 +47,7 @@ __device__ inline bool q_ray_candidate(const QArgs &a, uint32_t j, V3 begin, V3 
     uint4 m = a.meta[j];
     if (m.w != a.space) return false;
     if (!(m.y & a.mask)) return false; // _can_collide_with: layer & mask (bodies only exist here)
+    if ((a.flags & BPC_RAY_PICK) && ((m.x >> 8) & BF_NOT_PICKABLE)) return false; // pick_ray && !is_ray_pickable()
     if (a.ex.n && q_excluded(a.ex, j)) return false;
     BodyXf bx = a.xf[j];
     X3 xf(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));

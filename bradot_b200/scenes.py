@@ -46,6 +46,7 @@ HINGE_DEFAULTS = np.array([0.3, -np.pi, np.pi, 0.3, 0.9, 1.0, 0.0, 0.0], np.floa
 # mode REPLACE, bits 8..13 axis locks (PhysicsServer3D::BodyAxis: linear x y z, angular x y z)
 # bits 16..23: body_set_max_contacts_reported
 BODY_LIN_DAMP_REPLACE, BODY_ANG_DAMP_REPLACE, BODY_LOCK_SHIFT, BODY_REPORT_SHIFT = 16, 32, 8, 16
+BODY_NOT_PICKABLE = 128   # bit7: body_set_ray_pickable(false)
 IDENT12 = np.array([1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0], dtype=np.float32)
 
 

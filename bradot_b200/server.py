@@ -403,12 +403,12 @@ class PhysicsServerCUDA:
         cf = np.ascontiguousarray(cf, np.float32).reshape(-1, 4, 16)
         self._check(self.lib.bpc_pairs_write(self.ctx, len(ids), _ptr(ids), _ptr(pf), _ptr(cf)))
 
-    def intersect_rays(self, from_to, space=0, collision_mask=0xFFFFFFFF, hit_from_inside=False, hit_back_faces=True):
+    def intersect_rays(self, from_to, space=0, collision_mask=0xFFFFFFFF, hit_from_inside=False, hit_back_faces=True, pick_ray=False):
         """Batched PhysicsDirectSpaceState3D.intersect_ray: returns (hit bool[n], body int32[n], position (n,3), normal (n,3))."""
         r = np.ascontiguousarray(from_to, np.float32).reshape(-1, 6)
         out = np.zeros(len(r), RAY_RESULT_DT)
         self._check(self.lib.bpc_space_intersect_rays(self.ctx, int(space), len(r), _ptr(r), ctypes.c_uint(collision_mask),
-                                                      (1 if hit_from_inside else 0) | (2 if hit_back_faces else 0), _ptr(out)))
+                                                      (1 if hit_from_inside else 0) | (2 if hit_back_faces else 0) | (4 if pick_ray else 0), _ptr(out)))
         return out["hit"] != 0, out["body"].copy(), out["position"].copy(), out["normal"].copy()
 
     def intersect_points(self, points, space=0, collision_mask=0xFFFFFFFF, max_results=32):

@@ -265,7 +265,7 @@ struct BpcExcludeScope {
 	}
 };
 
-int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces) {
+int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces, bool p_pick_ray) {
 	ERR_FAIL_NULL_V(server, 0);
 	ERR_FAIL_COND_V(p_from_to.size() % 2, 0);
 	server->_flush_pending();
@@ -279,7 +279,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 	}
 	LocalVector<bpc_ray_result> out;
 	out.resize(n);
-	ERR_FAIL_COND_V_MSG(bpc_space_intersect_rays(server->ctx, space_handle, n, in.ptr(), p_collision_mask, (p_hit_from_inside ? BPC_RAY_HIT_FROM_INSIDE : 0) | (p_hit_back_faces ? BPC_RAY_HIT_BACK_FACES : 0), out.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_rays(server->ctx, space_handle, n, in.ptr(), p_collision_mask, (p_hit_from_inside ? BPC_RAY_HIT_FROM_INSIDE : 0) | (p_hit_back_faces ? BPC_RAY_HIT_BACK_FACES : 0) | (p_pick_ray ? BPC_RAY_PICK : 0), out.ptr()) < 0, 0, bpc_last_error(server->ctx));
 	r_results.resize(n);
 	r_hit.resize(n);
 	int hits = 0;
@@ -462,7 +462,7 @@ bool BradotPhysicsDirectSpaceStateCUDA::rest_info(const ShapeParameters &p_param
 }
 
 bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_parameters, RayResult &r_result) {
-	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas || p_parameters.pick_ray, false, "BradotPhysicsCUDA: intersect_ray with areas or pick_ray is not supported yet.");
+	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, false, "BradotPhysicsCUDA: intersect_ray with areas is not supported yet.");
 	if (!p_parameters.collide_with_bodies) {
 		return false;
 	}
@@ -475,7 +475,7 @@ bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_par
 	ft.push_back(p_parameters.to);
 	LocalVector<RayResult> res;
 	LocalVector<bool> hit;
-	if (intersect_rays_batch(ft, p_parameters.collision_mask, p_parameters.hit_from_inside, res, hit, p_parameters.hit_back_faces) != 1) {
+	if (intersect_rays_batch(ft, p_parameters.collision_mask, p_parameters.hit_from_inside, res, hit, p_parameters.hit_back_faces, p_parameters.pick_ray) != 1) {
 		return false;
 	}
 	r_result = res[0];
@@ -529,7 +529,7 @@ void BradotPhysicsServerCUDA::_fill_desc(const Body *p_body, bpc_body_desc &r_de
 	r_desc.mode = (uint32_t)b->mode;
 	r_desc.shape = shape ? _shape_handle(shape) : 0;
 	r_desc.flags = (b->can_sleep ? 1 : 0) | (b->ccd ? 2 : 0) | (b->lin_damp_replace ? 16 : 0) | (b->ang_damp_replace ? 32 : 0) |
-			(b->omit_force_integration ? 64 : 0) | ((b->locked_axis & 63) << 8);
+			(b->omit_force_integration ? 64 : 0) | (b->ray_pickable ? 0 : 128) | ((b->locked_axis & 63) << 8);
 	_xf_to_floats(b->xf, r_desc.xf);
 	_xf_to_floats(b->shape_xf, r_desc.shape_xf);
 	r_desc.linvel[0] = b->linvel.x; r_desc.linvel[1] = b->linvel.y; r_desc.linvel[2] = b->linvel.z;
@@ -878,6 +878,14 @@ Variant BradotPhysicsServerCUDA::body_get_state(RID p_body, BodyState p_state) c
 		case BODY_STATE_SLEEPING: return st[18] == 0.f;
 		default: return Variant();
 	}
+}
+
+// body_set_ray_pickable (bradot_physics_server_3d.cpp:907-911): only rays cast with RayParameters::pick_ray pass such a body by
+void BradotPhysicsServerCUDA::body_set_ray_pickable(RID p_body, bool p_enable) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->ray_pickable = p_enable;
+	_body_changed(body);
 }
 
 void BradotPhysicsServerCUDA::body_set_enable_continuous_collision_detection(RID p_body, bool p_enable) {

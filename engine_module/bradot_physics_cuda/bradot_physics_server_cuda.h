@@ -35,7 +35,7 @@ public:
 	int space_handle = -1;
 
 	virtual bool intersect_ray(const RayParameters &p_parameters, RayResult &r_result) override;
-	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces = true);
+	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces = true, bool p_pick_ray = false);
 	virtual int intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
 	virtual int intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
 	virtual bool cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info = nullptr) override;
@@ -132,6 +132,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		uint32_t layer = 1, mask = 1;
 		bool can_sleep = true;
 		bool ccd = false;
+		bool ray_pickable = true;
 		bool omit_force_integration = false;
 		bool lin_damp_replace = false, ang_damp_replace = false;
 		uint32_t locked_axis = 0;
@@ -274,6 +275,7 @@ public:
 	virtual real_t shape_get_custom_solver_bias(RID p_shape) const override;
 	virtual void shape_set_margin(RID p_shape, real_t p_margin) override;
 	virtual real_t shape_get_margin(RID p_shape) const override;
+	virtual void body_set_ray_pickable(RID p_body, bool p_enable) override;
 	virtual void body_set_user_flags(RID p_body, uint32_t p_flags) override;
 	virtual uint32_t body_get_user_flags(RID p_body) const override;
 	virtual void body_set_contacts_reported_depth_threshold(RID p_body, real_t p_threshold) override;

@@ -32,7 +32,8 @@ enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1, BPC_JOINT_CONE_TWIST = 2, BPC_JOI
  * (P3D/bradot_physics_server_3d.cpp:438-760). */
 typedef struct bpc_body_desc {
     /* flags: bit0 can_sleep, bit1 continuous collision detection, bit2 start asleep, bit4 / bit5 linear / angular damp mode
-     * REPLACE (BODY_PARAM_*_DAMP_MODE, P3D/bradot_body_3d.cpp:586-606), bit6 omit force integration, bits 8..13 axis locks
+     * REPLACE (BODY_PARAM_*_DAMP_MODE, P3D/bradot_body_3d.cpp:586-606), bit6 omit force integration, bit7 NOT ray pickable
+     * (body_set_ray_pickable(false); only rays cast with BPC_RAY_PICK care), bits 8..13 axis locks
      * in PhysicsServer3D::BodyAxis order (body_set_axis_lock, P3D/bradot_body_3d.cpp:685-699).
      * bit2 is kept as given: the body sleeps until something wakes it.  (The reference would wake it on its first step:
      * every body whose shapes were just added has a pending shape update, and BradotBody3D::_shapes_changed ends in
@@ -308,7 +309,7 @@ int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order);
  * one space -- closest hit along each segment, bodies whose collision layer meets collision_mask, a shape the ray starts
  * inside is ignored unless BPC_RAY_HIT_FROM_INSIDE.  from_to: n x (from xyz, to xyz), host; out: n records, host.
  * `body` is the body slot (what the engine module maps back to a RID / ObjectID), -1 for a miss.
- * Exclude lists: bpc_space_set_query_exclude below.  Not built: areas, pick_ray, face_index. */
+ * Exclude lists: bpc_space_set_query_exclude below.  Not built: areas, face_index. */
 typedef struct bpc_ray_result {
     int32_t hit;
     int32_t body;
@@ -316,6 +317,7 @@ typedef struct bpc_ray_result {
     float normal[3];
 } bpc_ray_result;
 #define BPC_RAY_HIT_FROM_INSIDE 1
+#define BPC_RAY_PICK 4 /* RayParameters::pick_ray: bodies that are not ray pickable are passed through (P3D/bradot_space_3d.cpp:134) */
 #define BPC_RAY_HIT_BACK_FACES 2 /* RayParameters::hit_back_faces (default on in the engine): a two-sided triangle mesh is also hit from behind */
 int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *from_to, unsigned collision_mask, int flags,
                              bpc_ray_result *out);

@@ -185,6 +185,7 @@ struct World {
 	BradotPhysicsServer3D *ps = nullptr;
 	std::vector<RID> spaces, shapes, bodies, joints, areas;
 	std::vector<char> area_freed;
+	bool any_unpickable = false; // some body has body_set_ray_pickable(false): the ray dumps also hold "rays_pick"
 	std::vector<BradotBody3D *> body_ptr;
 	std::map<const BradotBody3D *, int> body_index;
 	std::vector<uint32_t> body_space;
@@ -467,11 +468,14 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 	}
 	size_t n = rays.size() / 6;
 	std::vector<float> out(n * 8, 0.f);
+	for (int pick = 0; pick < (w.any_unpickable ? 2 : 1); pick++) { // "rays_pick": the same rays with RayParameters::pick_ray
+	std::fill(out.begin(), out.end(), 0.f);
 	for (size_t i = 0; i < n; i++) {
 		PhysicsDirectSpaceState3D::RayParameters rp;
 		rp.from = Vector3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]);
 		rp.to = Vector3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
 		rp.collision_mask = 0xffffffffu;
+		rp.pick_ray = pick != 0;
 		PhysicsDirectSpaceState3D::RayResult rr;
 		bool hit = ds && ds->intersect_ray(rp, rr);
 		out[i * 8 + 0] = hit ? 1.f : 0.f;
@@ -487,7 +491,8 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 			out[i * 8 + 7] = rr.normal.z;
 		}
 	}
-	d.arr("rays", step, "f4", { (uint64_t)n, 8 }, out.data(), out.size() * 4);
+	d.arr(pick ? "rays_pick" : "rays", step, "f4", { (uint64_t)n, 8 }, out.data(), out.size() * 4);
+	}
 	// intersect_point (bradot_space_3d.cpp:62-107) at every ray's origin: count, then up to 8 body indices
 	std::vector<int32_t> pts(n * 9, -1);
 	for (size_t i = 0; i < n; i++) {
@@ -997,6 +1002,10 @@ int main(int argc, char **argv) {
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, (b.flags & 1) != 0);
 		if (b.flags & 2) {
 			ps->body_set_enable_continuous_collision_detection(body, true);
+		}
+		if (b.flags & 128) { // bit7: not ray pickable
+			ps->body_set_ray_pickable(body, false);
+			w.any_unpickable = true;
 		}
 		if (b.flags & 16) {
 			ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_LINEAR_DAMP_MODE, PhysicsServer3D::BODY_DAMP_MODE_REPLACE);

@@ -56,6 +56,37 @@ def test_intersect_rays_convex_hulls():
     assert _compare(sc, _rays(4000, 6, 4.0, 8.0), 50, [1, 25, 49]) > 2000
 
 
+def test_intersect_rays_pick_ray_passes_unpickable_bodies():
+    """RayParameters::pick_ray with body_set_ray_pickable(false) on every third body (bradot_space_3d.cpp:134): those bodies are
+    passed through by picking rays and hit by ordinary ones, as in the reference."""
+    parity_needed()
+    sc = scenes.mixed_pile(4, half=3.0)
+    dyn = np.nonzero(sc.bodies["mode"] == scenes.MODE_RIGID)[0]
+    sc.bodies["flags"][dyn[::3]] |= scenes.BODY_NOT_PICKABLE
+    sc.bodies["flags"][0] |= scenes.BODY_NOT_PICKABLE         # and one of the container's planes
+    rays = _rays(3000, 9, 3.5, 6.0)
+    _, dump = parity.run_oracle(sc, 40, dump_from=0, dump_every=1, rays=rays)
+    ps = parity.new_server(sc, dump)
+    differ = 0
+    for k in (1, 20, 39):
+        parity.load_state(ps, dump, k)
+        for name, pick in (("rays", False), ("rays_pick", True)):
+            hit, body, pos, nrm = ps.intersect_rays(rays, pick_ray=pick)
+            ref = dump[(name, k)]
+            rhit = ref[:, 0] > 0
+            assert (hit == rhit).mean() > 0.999, (k, name)
+            both = hit & rhit
+            agree = body[both] == ref[both, 1].astype(np.int64)
+            assert agree.mean() > 0.999, (k, name)
+            sel = np.nonzero(both)[0][agree]
+            assert np.max(np.abs(pos[sel] - ref[sel, 2:5])) < POS_TOL, (k, name)
+            if pick:
+                assert not np.any((sc.bodies["flags"][body[hit]] & scenes.BODY_NOT_PICKABLE) != 0)
+        differ += int((dump[("rays", k)][:, 1] != dump[("rays_pick", k)][:, 1]).sum())
+    ps.finish()
+    assert differ > 300
+
+
 def test_intersect_rays_height_map():
     """BradotHeightMapShape3D::intersect_segment (bradot_shape_3d.cpp:1950-2008; the cell walk of _intersect_grid_segment,
     :1810-1948): rays over the height-map scene -- steep ones that stay inside one cell, long oblique ones that walk many
