@@ -126,6 +126,7 @@ struct SpaceParams {
 #define AF_MONITOR_CB 2u
 #define AF_GRAVITY_POINT 4u
 #define AF_AREA_MONITOR_CB 8u
+#define AF_PICKABLE 16u // area_set_ray_pickable(true); an area is not pickable until told so (bradot_area_3d.cpp:343)
 #define AF_ALIVE 0x100u
 #define AF_MOVED 0x200u
 #define AREA_EVENT_CAP (1u << 20)

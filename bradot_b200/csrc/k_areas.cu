@@ -203,7 +203,7 @@ static int area_from_desc(bpc_context *ctx, const bpc_area_desc &d, AreaRec &r) 
     r.space = (uint32_t)d.space;
     r.layer = d.layer;
     r.mask = d.mask;
-    r.flags = (d.flags & 15u) | AF_ALIVE | AF_MOVED;
+    r.flags = (d.flags & 31u) | AF_ALIVE | AF_MOVED;
     r.priority = d.priority;
     r.gravity_mode = (uint32_t)d.gravity_mode;
     r.lin_damp_mode = (uint32_t)d.linear_damp_mode;

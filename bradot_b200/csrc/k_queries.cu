@@ -33,6 +33,9 @@ struct QArgs {
     const uint32_t *big;
     const uint32_t *big_start;
     QExclude ex;
+    // collide_with_areas (BPC_QUERY_AREAS): the areas of the space, tested one by one after the bodies (they are few)
+    const AreaRec *areas;
+    const uint32_t *area_list, *area_start;
 };
 
 struct RayBest {
@@ -98,6 +101,45 @@ __device__ inline bool q_ray_candidate(const QArgs &a, uint32_t j, V3 begin, V3 
     return false;
 }
 
+// an area as a candidate of the same loop (the answer's `body` is -2 - area index); Transform3D::affine_inverse of the area
+// times that of its shape in the reference, of the product here
+__device__ inline bool q_ray_area(const QArgs &a, uint32_t ai, V3 begin, V3 end, V3 normal, RayBest &best) {
+    const AreaRec &ar = a.areas[ai];
+    if (!(ar.flags & AF_ALIVE) || !(ar.layer & a.mask)) return false;
+    if ((a.flags & BPC_RAY_PICK) && !(ar.flags & AF_PICKABLE)) return false;
+    X3 to_world(M3(f4v(ar.s0), f4v(ar.s1), f4v(ar.s2)), f4v(ar.so));
+    X3 inv_xform = affine_inverse(to_world);
+    V3 local_from = xform(inv_xform, begin), local_to = xform(inv_xform, end);
+    QShape s;
+    s.type = ar.shape_type;
+    s.p = ar.shape_p;
+    if (s.type >= SH_CONVEX) s.mesh = a.pools.meshes[__float_as_uint(s.p.x)];
+    if (q_shape_point_inside(a.pools, s, local_from)) {
+        if (a.flags & 1u) {
+            best.min_d = 0.f;
+            best.point = begin;
+            best.normal = V3();
+            best.body = (uint32_t)(-2 - (int)ai);
+            best.collided = true;
+            return true;
+        }
+        return false;
+    }
+    RayHit h;
+    if (q_shape_segment(a.pools, s, local_from, local_to, h, (a.flags & BPC_RAY_HIT_BACK_FACES) != 0)) {
+        V3 p = xform(to_world, h.point);
+        float ld = dot(normal, p);
+        if (ld < best.min_d) {
+            best.min_d = ld;
+            best.point = p;
+            best.normal = normalized(xform_inv(inv_xform.b, h.normal));
+            best.body = (uint32_t)(-2 - (int)ai);
+            best.collided = true;
+        }
+    }
+    return false;
+}
+
 __global__ void __launch_bounds__(Q_THREADS) k_intersect_rays(QArgs a) {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= a.n_rays) return;
@@ -107,7 +149,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_rays(QArgs a) {
     best.min_d = 1e10f;
     best.collided = false;
     best.body = 0xffffffffu;
-    bool done = false;
+    bool done = (a.flags & BPC_QUERY_NO_BODIES) != 0;
     for (uint32_t k = a.big_start[a.space], ke = a.big_start[a.space + 1]; k < ke && !done; k++) done = q_ray_candidate(a, a.big[k], begin, end, normal, best);
     const float grow = 1e-4f; // the box test only nominates candidates: err on the generous side
     if (!done && a.n_tree == 1) {
@@ -145,6 +187,10 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_rays(QArgs a) {
                 node = stack[--sp];
             }
         }
+    }
+    if ((a.flags & BPC_QUERY_AREAS) && !(best.collided && best.min_d == 0.f && (a.flags & 1u))) {
+        bool stop = false;
+        for (uint32_t k = a.area_start[a.space], ke = a.area_start[a.space + 1]; k < ke && !stop; k++) stop = q_ray_area(a, a.area_list[k], begin, end, normal, best);
     }
     bpc_ray_result o;
     o.hit = best.collided ? 1 : 0;
@@ -188,14 +234,30 @@ __device__ inline void q_point_candidate(const PArgs &a, uint32_t j, V3 point, u
     cc++;
 }
 
+__device__ inline void q_point_area(const PArgs &a, uint32_t ai, V3 point, uint32_t r, int &cc) {
+    if (cc >= (int)a.max_results) return;
+    const AreaRec &ar = a.q.areas[ai];
+    if (!(ar.flags & AF_ALIVE) || !(ar.layer & a.q.mask)) return;
+    X3 inv_xform = affine_inverse(X3(M3(f4v(ar.s0), f4v(ar.s1), f4v(ar.s2)), f4v(ar.so)));
+    QShape s;
+    s.type = ar.shape_type;
+    s.p = ar.shape_p;
+    if (s.type >= SH_CONVEX) s.mesh = a.q.pools.meshes[__float_as_uint(s.p.x)];
+    if (!q_shape_point_inside(a.q.pools, s, xform(inv_xform, point))) return;
+    a.bodies[(size_t)r * a.max_results + cc] = -2 - (int32_t)ai;
+    cc++;
+}
+
 __global__ void __launch_bounds__(Q_THREADS) k_intersect_points(PArgs a) {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= a.q.n_rays) return;
     V3 p(a.q.rays[r * 3 + 0], a.q.rays[r * 3 + 1], a.q.rays[r * 3 + 2]);
     int cc = 0;
-    for (uint32_t k = a.q.big_start[a.q.space], ke = a.q.big_start[a.q.space + 1]; k < ke; k++) q_point_candidate(a, a.q.big[k], p, r, cc);
+    const bool bodies = !(a.q.flags & BPC_QUERY_NO_BODIES);
+    for (uint32_t k = a.q.big_start[a.q.space], ke = a.q.big_start[a.q.space + 1]; k < ke && bodies; k++) q_point_candidate(a, a.q.big[k], p, r, cc);
     const float grow = 1e-4f;
-    if (a.q.n_tree == 1) {
+    if (!bodies) {
+    } else if (a.q.n_tree == 1) {
         q_point_candidate(a, __float_as_uint(a.q.leaf_min[0].w), p, r, cc);
     } else if (a.q.n_tree > 1) {
         uint32_t stack[128]; // as deep as the traversal of the step: key length plus the index tie-break
@@ -227,6 +289,9 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_points(PArgs a) {
             }
         }
     }
+    if (a.q.flags & BPC_QUERY_AREAS) {
+        for (uint32_t k = a.q.area_start[a.q.space], ke = a.q.area_start[a.q.space + 1]; k < ke; k++) q_point_area(a, a.q.area_list[k], p, r, cc);
+    }
     a.counts[r] = cc;
 }
 
@@ -251,6 +316,10 @@ static void q_fill(bpc_context *ctx, QArgs &a, int space, int n, unsigned mask, 
     a.big_start = ctx->big_start.p;
     a.ex.ids = ctx->q_exclude.p;
     a.ex.n = ctx->n_q_exclude;
+    a.areas = ctx->d_areas.p;
+    a.area_list = ctx->area_list.p;
+    a.area_start = ctx->area_start.p;
+    if (ctx->h_areas.empty()) a.flags &= ~(uint32_t)BPC_QUERY_AREAS; // no area was ever made: nothing to walk
 }
 
 // ShapeParameters / RayParameters / PointParameters ::exclude (servers/physics_server_3d.h:139-201): the bodies every query of
@@ -286,8 +355,8 @@ extern "C" int bpc_space_set_query_exclude(bpc_context *ctx, const int32_t *bodi
     return 0;
 }
 
-extern "C" int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int max_results,
-                                          int32_t *out_counts, int32_t *out_bodies) {
+extern "C" int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int flags,
+                                          int max_results, int32_t *out_counts, int32_t *out_bodies) {
     if (!ctx) return -1;
     if (space < 0 || (size_t)space >= ctx->spaces.size()) {
         ctx->err = "bpc_space_intersect_points: no such space";
@@ -307,8 +376,9 @@ extern "C" int bpc_space_intersect_points(bpc_context *ctx, int space, int n, co
         ctx->err = "bpc_space_intersect_points: out of device memory";
         return -1;
     }
+    if ((flags & BPC_QUERY_AREAS) && bpc_flush_area_tables(ctx)) return -1;
     PArgs a;
-    q_fill(ctx, a.q, space, n, collision_mask, 0);
+    q_fill(ctx, a.q, space, n, collision_mask, flags);
     a.q.rays = ctx->staging.p;
     a.q.out = nullptr;
     a.max_results = (uint32_t)max_results;
@@ -349,6 +419,7 @@ extern "C" int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, cons
     float *d_in = ctx->staging.p;
     bpc_ray_result *d_out = (bpc_ray_result *)(ctx->staging.p + ((in_floats + 3) & ~(size_t)3));
     BPC_CHECK(cudaMemcpyAsync(d_in, from_to, in_floats * sizeof(float), cudaMemcpyHostToDevice, st));
+    if ((flags & BPC_QUERY_AREAS) && bpc_flush_area_tables(ctx)) return -1;
     QArgs a;
     q_fill(ctx, a, space, n, collision_mask, flags);
     a.rays = d_in;

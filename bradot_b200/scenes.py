@@ -38,7 +38,7 @@ AREA_DT = np.dtype([("space", "<i4"), ("shape", "<i4"), ("flags", "<u4"), ("prio
                     ("layer", "<u4"), ("mask", "<u4"), ("gravity_mode", "<i4"), ("linear_damp_mode", "<i4"), ("angular_damp_mode", "<i4"),
                     ("gravity", "<f4"), ("gravity_vector", "<f4", 3), ("point_unit_distance", "<f4"), ("linear_damp", "<f4"),
                     ("angular_damp", "<f4"), ("reserved", "<u4")])
-AREA_MONITORABLE, AREA_MONITOR_CB, AREA_GRAVITY_POINT, AREA_AREA_MONITOR_CB = 1, 2, 4, 8
+AREA_MONITORABLE, AREA_MONITOR_CB, AREA_GRAVITY_POINT, AREA_AREA_MONITOR_CB, AREA_PICKABLE = 1, 2, 4, 8, 16
 JOINT_NO_COLLIDE, JOINT_USE_LIMIT, JOINT_ENABLE_MOTOR, JOINT_HAS_PARAMS = 1, 2, 4, 8
 PIN_DEFAULTS = np.array([0.3, 1.0, 0.0, 0, 0, 0, 0, 0], np.float32)
 HINGE_DEFAULTS = np.array([0.3, -np.pi, np.pi, 0.3, 0.9, 1.0, 0.0, 0.0], np.float32)   # upper = -pi, lower = pi: the reference's "no limit"

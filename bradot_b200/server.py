@@ -120,7 +120,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_test_segment_math.argtypes = [vp, ci, ci, vp, vp]
     lib.bpc_step.argtypes = [vp, cf]
     lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
-    lib.bpc_space_intersect_points.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp, vp]
+    lib.bpc_space_intersect_points.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, ci, vp, vp]
     lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
     lib.bpc_space_collide_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
     lib.bpc_space_set_query_exclude.argtypes = [vp, vp, ci]
@@ -403,21 +403,23 @@ class PhysicsServerCUDA:
         cf = np.ascontiguousarray(cf, np.float32).reshape(-1, 4, 16)
         self._check(self.lib.bpc_pairs_write(self.ctx, len(ids), _ptr(ids), _ptr(pf), _ptr(cf)))
 
-    def intersect_rays(self, from_to, space=0, collision_mask=0xFFFFFFFF, hit_from_inside=False, hit_back_faces=True, pick_ray=False):
+    def intersect_rays(self, from_to, space=0, collision_mask=0xFFFFFFFF, hit_from_inside=False, hit_back_faces=True, pick_ray=False, areas=False, bodies=True):
         """Batched PhysicsDirectSpaceState3D.intersect_ray: returns (hit bool[n], body int32[n], position (n,3), normal (n,3))."""
         r = np.ascontiguousarray(from_to, np.float32).reshape(-1, 6)
         out = np.zeros(len(r), RAY_RESULT_DT)
         self._check(self.lib.bpc_space_intersect_rays(self.ctx, int(space), len(r), _ptr(r), ctypes.c_uint(collision_mask),
-                                                      (1 if hit_from_inside else 0) | (2 if hit_back_faces else 0) | (4 if pick_ray else 0), _ptr(out)))
+                                                      (1 if hit_from_inside else 0) | (2 if hit_back_faces else 0) | (4 if pick_ray else 0) | (8 if areas else 0) | (0 if bodies else 16), _ptr(out)))
         return out["hit"] != 0, out["body"].copy(), out["position"].copy(), out["normal"].copy()
 
-    def intersect_points(self, points, space=0, collision_mask=0xFFFFFFFF, max_results=32):
-        """Batched PhysicsDirectSpaceState3D.intersect_point: (counts int32[n], bodies int32[n, max_results], -1 padded)."""
+    def intersect_points(self, points, space=0, collision_mask=0xFFFFFFFF, max_results=32, areas=False, bodies=True):
+        """Batched PhysicsDirectSpaceState3D.intersect_point: (counts int32[n], bodies int32[n, max_results], -1 padded);
+        with `areas`, areas are listed too, as -2 - area index."""
+        with_bodies = bodies
         p = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
         counts = np.zeros(len(p), np.int32)
         bodies = np.full((len(p), max_results), -1, np.int32)
-        self._check(self.lib.bpc_space_intersect_points(self.ctx, int(space), len(p), _ptr(p), ctypes.c_uint(collision_mask), int(max_results),
-                                                        _ptr(counts), _ptr(bodies)))
+        self._check(self.lib.bpc_space_intersect_points(self.ctx, int(space), len(p), _ptr(p), ctypes.c_uint(collision_mask),
+                                                        (8 if areas else 0) | (0 if with_bodies else 16), int(max_results), _ptr(counts), _ptr(bodies)))
         return counts, bodies
 
     def intersect_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=32, margin=0.0):

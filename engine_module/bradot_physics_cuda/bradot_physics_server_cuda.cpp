@@ -265,7 +265,7 @@ struct BpcExcludeScope {
 	}
 };
 
-int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces, bool p_pick_ray) {
+int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces, bool p_pick_ray, bool p_with_areas, bool p_with_bodies) {
 	ERR_FAIL_NULL_V(server, 0);
 	ERR_FAIL_COND_V(p_from_to.size() % 2, 0);
 	server->_flush_pending();
@@ -279,12 +279,14 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 	}
 	LocalVector<bpc_ray_result> out;
 	out.resize(n);
-	ERR_FAIL_COND_V_MSG(bpc_space_intersect_rays(server->ctx, space_handle, n, in.ptr(), p_collision_mask, (p_hit_from_inside ? BPC_RAY_HIT_FROM_INSIDE : 0) | (p_hit_back_faces ? BPC_RAY_HIT_BACK_FACES : 0) | (p_pick_ray ? BPC_RAY_PICK : 0), out.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_rays(server->ctx, space_handle, n, in.ptr(), p_collision_mask, (p_hit_from_inside ? BPC_RAY_HIT_FROM_INSIDE : 0) | (p_hit_back_faces ? BPC_RAY_HIT_BACK_FACES : 0) | (p_pick_ray ? BPC_RAY_PICK : 0) | (p_with_areas ? BPC_QUERY_AREAS : 0) | (p_with_bodies ? 0 : BPC_QUERY_NO_BODIES), out.ptr()) < 0, 0, bpc_last_error(server->ctx));
 	r_results.resize(n);
 	r_hit.resize(n);
 	int hits = 0;
 	for (int i = 0; i < n; i++) {
-		r_hit[i] = out[i].hit != 0 && out[i].body >= 0 && (uint32_t)out[i].body < server->body_of_slot.size() && server->body_of_slot[out[i].body];
+		const int area_handle = -2 - out[i].body; // an area answers as -2 - its index
+		const bool is_area = out[i].hit != 0 && out[i].body <= -2 && (uint32_t)area_handle < server->area_of_handle.size() && server->area_of_handle[area_handle];
+		r_hit[i] = is_area || (out[i].hit != 0 && out[i].body >= 0 && (uint32_t)out[i].body < server->body_of_slot.size() && server->body_of_slot[out[i].body]);
 		if (!r_hit[i]) {
 			continue;
 		}
@@ -292,8 +294,8 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 		RayResult &r = r_results[i];
 		r.position = Vector3(out[i].position[0], out[i].position[1], out[i].position[2]);
 		r.normal = Vector3(out[i].normal[0], out[i].normal[1], out[i].normal[2]);
-		r.rid = server->body_of_slot[out[i].body]->self;
-		r.collider_id = server->body_of_slot[out[i].body]->instance_id;
+		r.rid = is_area ? server->area_of_handle[area_handle]->self : server->body_of_slot[out[i].body]->self;
+		r.collider_id = is_area ? server->area_of_handle[area_handle]->instance_id : server->body_of_slot[out[i].body]->instance_id;
 		r.collider = r.collider_id.is_valid() ? ObjectDB::get_instance(r.collider_id) : nullptr;
 		r.shape = 0;
 		r.face_index = -1;
@@ -303,8 +305,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 
 int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) {
 	ERR_FAIL_NULL_V(server, 0);
-	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, 0, "BradotPhysicsCUDA: intersect_point with areas is not supported yet.");
-	if (p_result_max <= 0 || !p_parameters.collide_with_bodies) {
+	if (p_result_max <= 0 || (!p_parameters.collide_with_bodies && !p_parameters.collide_with_areas)) {
 		return 0;
 	}
 	server->_flush_pending();
@@ -315,9 +316,20 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_
 	int32_t count = 0;
 	LocalVector<int32_t> slots;
 	slots.resize(max_r);
-	ERR_FAIL_COND_V_MSG(bpc_space_intersect_points(server->ctx, space_handle, 1, p, p_parameters.collision_mask, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_points(server->ctx, space_handle, 1, p, p_parameters.collision_mask, (p_parameters.collide_with_areas ? BPC_QUERY_AREAS : 0) | (p_parameters.collide_with_bodies ? 0 : BPC_QUERY_NO_BODIES), max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
 	int cc = 0;
 	for (int i = 0; i < count; i++) {
+		if (slots[i] <= -2) { // an area
+			const int ah = -2 - slots[i];
+			if ((uint32_t)ah < server->area_of_handle.size() && server->area_of_handle[ah]) {
+				r_results[cc].rid = server->area_of_handle[ah]->self;
+				r_results[cc].collider_id = server->area_of_handle[ah]->instance_id;
+				r_results[cc].collider = r_results[cc].collider_id.is_valid() ? ObjectDB::get_instance(r_results[cc].collider_id) : nullptr;
+				r_results[cc].shape = 0;
+				cc++;
+			}
+			continue;
+		}
 		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size() || !server->body_of_slot[slots[i]]) {
 			continue;
 		}
@@ -462,8 +474,7 @@ bool BradotPhysicsDirectSpaceStateCUDA::rest_info(const ShapeParameters &p_param
 }
 
 bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_parameters, RayResult &r_result) {
-	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, false, "BradotPhysicsCUDA: intersect_ray with areas is not supported yet.");
-	if (!p_parameters.collide_with_bodies) {
+	if (!p_parameters.collide_with_bodies && !p_parameters.collide_with_areas) {
 		return false;
 	}
 	ERR_FAIL_NULL_V(server, false);
@@ -475,7 +486,7 @@ bool BradotPhysicsDirectSpaceStateCUDA::intersect_ray(const RayParameters &p_par
 	ft.push_back(p_parameters.to);
 	LocalVector<RayResult> res;
 	LocalVector<bool> hit;
-	if (intersect_rays_batch(ft, p_parameters.collision_mask, p_parameters.hit_from_inside, res, hit, p_parameters.hit_back_faces, p_parameters.pick_ray) != 1) {
+	if (intersect_rays_batch(ft, p_parameters.collision_mask, p_parameters.hit_from_inside, res, hit, p_parameters.hit_back_faces, p_parameters.pick_ray, p_parameters.collide_with_areas, p_parameters.collide_with_bodies) != 1) {
 		return false;
 	}
 	r_result = res[0];
@@ -1902,7 +1913,7 @@ void BradotPhysicsServerCUDA::_fill_area_desc(const Area *p_area, bpc_area_desc 
 	Shape *shape = shape_owner.get_or_null(p_area->shape);
 	r_desc.space = space ? space->handle : -1;
 	r_desc.shape = shape ? _shape_handle(shape) : -1;
-	r_desc.flags = (p_area->monitorable ? 1u : 0u) | (p_area->monitor_callback.is_valid() ? 2u : 0u) | (p_area->gravity_is_point ? 4u : 0u) |
+	r_desc.flags = (p_area->ray_pickable ? 16u : 0u) | (p_area->monitorable ? 1u : 0u) | (p_area->monitor_callback.is_valid() ? 2u : 0u) | (p_area->gravity_is_point ? 4u : 0u) |
 			(p_area->area_monitor_callback.is_valid() ? 8u : 0u);
 	r_desc.priority = p_area->priority;
 	_xf_to_floats(p_area->xf, r_desc.xf);
@@ -2208,6 +2219,7 @@ void BradotPhysicsServerCUDA::area_set_ray_pickable(RID p_area, bool p_enable) {
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
 	area->ray_pickable = p_enable;
+	_area_changed(area);
 }
 
 // BradotArea3D::call_queries (P3D/bradot_area_3d.cpp:232-271): what happened to each (area, body) since the last flush, summed

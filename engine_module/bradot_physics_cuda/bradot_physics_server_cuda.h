@@ -35,7 +35,7 @@ public:
 	int space_handle = -1;
 
 	virtual bool intersect_ray(const RayParameters &p_parameters, RayResult &r_result) override;
-	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces = true, bool p_pick_ray = false);
+	int intersect_rays_batch(const Vector<Vector3> &p_from_to, uint32_t p_collision_mask, bool p_hit_from_inside, LocalVector<RayResult> &r_results, LocalVector<bool> &r_hit, bool p_hit_back_faces = true, bool p_pick_ray = false, bool p_with_areas = false, bool p_with_bodies = true);
 	virtual int intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
 	virtual int intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) override;
 	virtual bool cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info = nullptr) override;
@@ -179,7 +179,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		Transform3D xf, shape_xf;
 		bool shape_disabled = false;
 		uint32_t layer = 1, mask = 1;
-		bool monitorable = false, ray_pickable = false, gravity_is_point = false;
+		bool monitorable = false, ray_pickable = false, gravity_is_point = false; // (BradotArea3D's constructor: not pickable, bradot_area_3d.cpp:343)
 		Callable monitor_callback, area_monitor_callback;
 		ObjectID instance_id;
 		int gravity_mode = 0, linear_damp_mode = 0, angular_damp_mode = 0, priority = 0;

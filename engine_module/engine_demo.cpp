@@ -358,6 +358,9 @@ int main(int argc, char **argv) {
 		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_ANGULAR_DAMP, a.angular_damp);
 		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_PRIORITY, a.priority);
 		ps->area_set_monitorable(ar, (a.flags & 1) != 0);
+		if (a.flags & 16) {
+			ps->area_set_ray_pickable(ar, true);
+		}
 		if (a.flags & 2) {
 			ps->area_set_monitor_callback(ar, callable_mp_static(&on_area_monitor).bind((int)i));
 		}

@@ -221,7 +221,9 @@ int bpc_contacts_read(bpc_context *ctx, int32_t *counts, int32_t *offsets, bpc_c
  * (by priority, with the reference's combine / replace rules), one with a monitor callback is told who enters and leaves.
  * flags: bit0 monitorable, bit1 a body monitor callback is set (events are raised), bit2 the gravity vector is a point
  * (in the area's space) bodies are pulled towards, bit3 an area monitor callback is set (it is told which monitorable
- * areas it overlaps: BradotArea2Pair3D, P3D/bradot_area_pair_3d.cpp:124-206; looked at in steps where one of the two moved).
+ * areas it overlaps: BradotArea2Pair3D, P3D/bradot_area_pair_3d.cpp:124-206; looked at in steps where one of the two moved),
+ * bit4 ray pickable (area_set_ray_pickable(true); without it rays cast with BPC_RAY_PICK pass the area by, which is how the
+ * reference's areas start out, P3D/bradot_area_3d.cpp:343).
  * Override modes are
  * PhysicsServer3D::AreaSpaceOverrideMode: 0 disabled, 1 combine, 2 combine-replace, 3 replace, 4 replace-combine.
  * Not built: wind (soft bodies only). */
@@ -309,7 +311,7 @@ int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order);
  * one space -- closest hit along each segment, bodies whose collision layer meets collision_mask, a shape the ray starts
  * inside is ignored unless BPC_RAY_HIT_FROM_INSIDE.  from_to: n x (from xyz, to xyz), host; out: n records, host.
  * `body` is the body slot (what the engine module maps back to a RID / ObjectID), -1 for a miss.
- * Exclude lists: bpc_space_set_query_exclude below.  Not built: areas, face_index. */
+ * Exclude lists: bpc_space_set_query_exclude below.  Not built: face_index. */
 typedef struct bpc_ray_result {
     int32_t hit;
     int32_t body;
@@ -317,6 +319,8 @@ typedef struct bpc_ray_result {
     float normal[3];
 } bpc_ray_result;
 #define BPC_RAY_HIT_FROM_INSIDE 1
+#define BPC_QUERY_AREAS 8      /* collide_with_areas (rays and points): areas answer as well; an area's `body` is -2 - its index */
+#define BPC_QUERY_NO_BODIES 16 /* collide_with_bodies = false */
 #define BPC_RAY_PICK 4 /* RayParameters::pick_ray: bodies that are not ray pickable are passed through (P3D/bradot_space_3d.cpp:134) */
 #define BPC_RAY_HIT_BACK_FACES 2 /* RayParameters::hit_back_faces (default on in the engine): a two-sided triangle mesh is also hit from behind */
 int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *from_to, unsigned collision_mask, int flags,
@@ -325,9 +329,11 @@ int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *fr
 /* PhysicsDirectSpaceState3D::intersect_point (servers/physics_server_3d.h:188-203; implementation
  * modules/bradot_physics_3d/bradot_space_3d.cpp:62-107), batched: for each of n points (xyz, host) the bodies whose shape
  * holds it.  out_counts: n; out_bodies: n x max_results body slots, -1 padded.  When more than max_results bodies hold a
- * point, which ones are listed follows this backend's tree order (the reference's follows its own BVH). */
-int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int max_results,
-                               int32_t *out_counts, int32_t *out_bodies);
+ * point, which ones are listed follows this backend's tree order (the reference's follows its own BVH).
+ * flags: BPC_QUERY_AREAS / BPC_QUERY_NO_BODIES (PointParameters::collide_with_areas / collide_with_bodies); areas are listed
+ * after the bodies, as -2 - area index. */
+int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int flags,
+                               int max_results, int32_t *out_counts, int32_t *out_bodies);
 
 /* PhysicsDirectSpaceState3D::intersect_shape (servers/physics_server_3d.h:183-205; implementation
  * modules/bradot_physics_3d/bradot_space_3d.cpp:208-262), batched: query i is shape handle shapes[i] (from bpc_shape_create*)

@@ -468,7 +468,17 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 	}
 	size_t n = rays.size() / 6;
 	std::vector<float> out(n * 8, 0.f);
-	for (int pick = 0; pick < (w.any_unpickable ? 2 : 1); pick++) { // "rays_pick": the same rays with RayParameters::pick_ray
+	std::map<RID, int> area_index;
+	for (size_t i = 0; i < w.areas.size(); i++) {
+		area_index[w.areas[i]] = (int)i;
+	}
+	// variants: "rays"; "rays_pick" (RayParameters::pick_ray, when some object is not pickable); with areas in the scene
+	// "rays_areas" (collide_with_areas; an area answers as -2 - its index) and "rays_areas_only" (no bodies, pick_ray)
+	for (int variant = 0; variant < 4; variant++) {
+	const int pick = variant == 1 || variant == 3;
+	if ((variant == 1 && !w.any_unpickable) || (variant >= 2 && w.areas.empty())) {
+		continue;
+	}
 	std::fill(out.begin(), out.end(), 0.f);
 	for (size_t i = 0; i < n; i++) {
 		PhysicsDirectSpaceState3D::RayParameters rp;
@@ -476,6 +486,8 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 		rp.to = Vector3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
 		rp.collision_mask = 0xffffffffu;
 		rp.pick_ray = pick != 0;
+		rp.collide_with_areas = variant >= 2;
+		rp.collide_with_bodies = variant != 3;
 		PhysicsDirectSpaceState3D::RayResult rr;
 		bool hit = ds && ds->intersect_ray(rp, rr);
 		out[i * 8 + 0] = hit ? 1.f : 0.f;
@@ -483,6 +495,10 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 		if (hit) {
 			auto it = rid_index.find(rr.rid);
 			out[i * 8 + 1] = it == rid_index.end() ? -1.f : (float)it->second;
+			auto ita = area_index.find(rr.rid);
+			if (ita != area_index.end()) {
+				out[i * 8 + 1] = (float)(-2 - ita->second);
+			}
 			out[i * 8 + 2] = rr.position.x;
 			out[i * 8 + 3] = rr.position.y;
 			out[i * 8 + 4] = rr.position.z;
@@ -491,7 +507,8 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 			out[i * 8 + 7] = rr.normal.z;
 		}
 	}
-	d.arr(pick ? "rays_pick" : "rays", step, "f4", { (uint64_t)n, 8 }, out.data(), out.size() * 4);
+	static const char *names[4] = { "rays", "rays_pick", "rays_areas", "rays_areas_only" };
+	d.arr(names[variant], step, "f4", { (uint64_t)n, 8 }, out.data(), out.size() * 4);
 	}
 	// intersect_point (bradot_space_3d.cpp:62-107) at every ray's origin: count, then up to 8 body indices
 	std::vector<int32_t> pts(n * 9, -1);
@@ -508,6 +525,24 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 		}
 	}
 	d.arr("points", step, "i4", { (uint64_t)n, 9 }, pts.data(), pts.size() * 4);
+	if (!w.areas.empty()) { // "points_areas": the same with collide_with_areas, up to 16 results, areas as -2 - index
+		std::vector<int32_t> pa(n * 17, -1);
+		for (size_t i = 0; i < n; i++) {
+			PhysicsDirectSpaceState3D::PointParameters pp;
+			pp.position = Vector3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]);
+			pp.collision_mask = 0xffffffffu;
+			pp.collide_with_areas = true;
+			PhysicsDirectSpaceState3D::ShapeResult sr[16];
+			int cc = ds ? ds->intersect_point(pp, sr, 16) : 0;
+			pa[i * 17] = cc;
+			for (int k = 0; k < cc; k++) {
+				auto it = rid_index.find(sr[k].rid);
+				auto ita = area_index.find(sr[k].rid);
+				pa[i * 17 + 1 + k] = it != rid_index.end() ? it->second : (ita != area_index.end() ? -2 - ita->second : -1);
+			}
+		}
+		d.arr("points_areas", step, "i4", { (uint64_t)n, 17 }, pa.data(), pa.size() * 4);
+	}
 	// intersect_shape (bradot_space_3d.cpp:208-262): query i uses shape i % 3 of {sphere 0.35, box (0.3, 0.2, 0.25), capsule r 0.2
 	// h 0.9} at the ray's origin, turned about the ray's direction by 0.37 i.  The transforms are dumped so that the other
 	// side asks with the same floats.
@@ -1126,6 +1161,9 @@ int main(int argc, char **argv) {
 		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_ANGULAR_DAMP, a.angular_damp);
 		ps->area_set_param(ar, PhysicsServer3D::AREA_PARAM_PRIORITY, a.priority);
 		ps->area_set_monitorable(ar, (a.flags & 1) != 0);
+		if (a.flags & 16) { // bit4: ray pickable (areas start out not pickable)
+			ps->area_set_ray_pickable(ar, true);
+		}
 		if (a.flags & 2) {
 			ps->area_set_monitor_callback(ar, callable_mp_static(&on_area_monitor).bind((int)i));
 		}

@@ -87,6 +87,47 @@ def test_intersect_rays_pick_ray_passes_unpickable_bodies():
     assert differ > 300
 
 
+def test_rays_and_points_with_areas():
+    """collide_with_areas / collide_with_bodies of intersect_ray and intersect_point (_can_collide_with, bradot_space_3d.cpp:45-60):
+    rays and points over the area scene answer with bodies and areas, with areas alone (picking rays: only some of the areas are
+    pickable), as the reference does; an area's answer is -2 - its index."""
+    parity_needed()
+    sc = scenes.area_zones()
+    pickable = [0, 2, 3, 5, 7]
+    sc.areas["flags"][pickable] |= scenes.AREA_PICKABLE
+    rng = np.random.default_rng(21)
+    n = 3000
+    frm = np.stack([rng.uniform(-3, 33, n), rng.uniform(0, 9, n), rng.uniform(-3, 3, n)], -1)
+    to = frm + rng.normal(size=(n, 3)) * np.array([6.0, 3.0, 2.0])
+    frm[:600] = sc.areas["xf"][rng.integers(0, len(sc.areas), 600), 9:12] + rng.normal(size=(600, 3)) * 0.6     # many start inside an area
+    rays = np.concatenate([frm, to], 1).astype(np.float32)
+    _, dump = parity.run_oracle(sc, 40, dump_from=0, dump_every=1, rays=rays)
+    ps = parity.new_server(sc, dump)
+    area_hits = 0
+    for k in (1, 20, 39):
+        parity.load_state(ps, dump, k)
+        for name, kw in (("rays", {}), ("rays_areas", dict(areas=True)), ("rays_areas_only", dict(areas=True, bodies=False, pick_ray=True))):
+            hit, body, pos, nrm = ps.intersect_rays(rays, **kw)
+            ref = dump[(name, k)]
+            rhit = ref[:, 0] > 0
+            assert (hit == rhit).mean() > 0.998, (k, name, int((hit != rhit).sum()))
+            both = hit & rhit
+            agree = body[both] == ref[both, 1].astype(np.int64)
+            assert agree.mean() > 0.998, (k, name, int((~agree).sum()))
+            sel = np.nonzero(both)[0][agree]
+            assert np.max(np.abs(pos[sel] - ref[sel, 2:5])) < POS_TOL and np.max(np.abs(nrm[sel] - ref[sel, 5:8])) < NRM_TOL, (k, name)
+            if name == "rays_areas_only":
+                assert np.all(body[hit] <= -2) and np.all(np.isin(-2 - body[hit], pickable))
+                area_hits += int(hit.sum())
+        counts, listed = ps.intersect_points(rays[:, 0:3], max_results=16, areas=True)
+        refp = dump[("points_areas", k)]
+        differ = sum(set(listed[i, :counts[i]].tolist()) != set(refp[i, 1:1 + refp[i, 0]].tolist()) for i in range(n))
+        assert differ <= 3, (k, differ)
+        assert (refp[:, 1:] <= -2).sum() > 400
+    ps.finish()
+    assert area_hits > 500
+
+
 def test_intersect_rays_height_map():
     """BradotHeightMapShape3D::intersect_segment (bradot_shape_3d.cpp:1950-2008; the cell walk of _intersect_grid_segment,
     :1810-1948): rays over the height-map scene -- steep ones that stay inside one cell, long oblique ones that walk many
