@@ -382,8 +382,8 @@ def cuda_arm(args):
     # ---------------- end-to-end arm: host buffers through the C ABI, fresh context, same schedule
     ps2, _ = settle_on_gpu(sc, settle, local, stream)
     forces_t = torch.zeros((nb, 6), dtype=torch.float32).pin_memory()   # pinned host buffers, as an engine would keep
-    xf_t = torch.zeros((nb, 12), dtype=torch.float32).pin_memory()
-    forces, xf_host = forces_t.numpy(), xf_t.numpy()
+    xf_t = [torch.zeros((nb, 12), dtype=torch.float32).pin_memory() for _ in range(2)]
+    forces, xf_host = forces_t.numpy(), [x.numpy() for x in xf_t]
     for _ in range(args.warmup):
         ps2.step(sc.dt)
     ps2.sync()
@@ -392,11 +392,18 @@ def cuda_arm(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     checksum = 0.0
-    for _ in range(args.steps):
+    # every step: H2D of the force rows, the step, D2H of every transform.  The read-back is the pipelined one of the C ABI
+    # (bpc_bodies_read_begin / _end, two pinned buffers): step k's transforms cross the bus while step k + 1 runs and are
+    # consumed one step later -- what an engine's flush_queries does with last tick's state.
+    for k in range(args.steps):
         ps2.bodies_write(server.FIELD_APPLIED_FORCE, forces)     # H2D: per-body force/torque accumulators
         ps2.step(sc.dt)
-        xf = ps2.bodies_read(server.FIELD_TRANSFORM, out=xf_host)  # D2H: every body transform (state sync)
-        checksum += float(xf[-1, 10])
+        ps2.bodies_read_end()                                      # step k - 1's transforms are on the host now
+        if k:
+            checksum += float(xf_host[(k - 1) & 1][-1, 10])
+        ps2.bodies_read_begin(server.FIELD_TRANSFORM, xf_host[k & 1])   # D2H: every body transform (state sync)
+    ps2.bodies_read_end()
+    checksum += float(xf_host[(args.steps - 1) & 1][-1, 10])
     e1.record()
     barrier()
     e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)

@@ -738,6 +738,16 @@ __global__ void k_unpack_forces(uint32_t n, const float *__restrict__ in, BodyFo
         if ((m & 0xffu) >= MODE_RIGID && !((m >> 8) & BF_ACTIVE)) meta[i].x = m | (BF_ACTIVE << 8);
     }
 }
+static int ensure_copy_stream(bpc_context *ctx) {
+    if (ctx->copy_stream) return 0;
+    BPC_CHECK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    BPC_CHECK(cudaStreamCreateWithFlags(&ctx->copy_stream_in, cudaStreamNonBlocking));
+    BPC_CHECK(cudaEventCreateWithFlags(&ctx->ev_packed, cudaEventDisableTiming));
+    BPC_CHECK(cudaEventCreateWithFlags(&ctx->ev_read_done, cudaEventDisableTiming));
+    BPC_CHECK(cudaEventCreateWithFlags(&ctx->ev_h2d, cudaEventDisableTiming));
+    BPC_CHECK(cudaEventCreateWithFlags(&ctx->ev_unpacked, cudaEventDisableTiming));
+    return 0;
+}
 static int staging_for(bpc_context *ctx, size_t floats) {
     ctx->staging.reserve(floats, false, ctx->stream);
     if (!ctx->staging.p) return fail(ctx, "out of device memory");
@@ -969,10 +979,19 @@ extern "C" int bpc_bodies_write(bpc_context *ctx, int field, int first, int n, c
             if (store(ctx, h, ctx->forces, first) || (woke && store(ctx, mt, ctx->meta, first))) return -1;
         } break;
         case BPC_FIELD_APPLIED_FORCE: {
-            if (staging_for(ctx, (size_t)n * 6)) return -1;
-            BPC_CHECK(cudaMemcpyAsync(ctx->staging.p, in, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-            k_unpack_forces<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->staging.p, ctx->forces.p + first, ctx->meta.p + first);
-            BPC_CHECK(cudaStreamSynchronize(ctx->stream)); // the caller may reuse its buffer right away
+            // the rows go up on the side stream while a step may still be running on the main one, which only waits for them
+            // before it unpacks; the host waits for the copy alone (the caller may reuse its buffer right away)
+            if (ensure_copy_stream(ctx)) return -1;
+            if (ctx->unpack_recorded) BPC_CHECK(cudaStreamWaitEvent(ctx->copy_stream_in, ctx->ev_unpacked, 0)); // the last unpack is done with the buffer
+            ctx->force_staging.reserve((size_t)n * 6, false, ctx->copy_stream_in);
+            if (!ctx->force_staging.p) return fail(ctx, "out of device memory");
+            BPC_CHECK(cudaMemcpyAsync(ctx->force_staging.p, in, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->copy_stream_in));
+            BPC_CHECK(cudaEventRecord(ctx->ev_h2d, ctx->copy_stream_in));
+            BPC_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->ev_h2d, 0));
+            k_unpack_forces<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->force_staging.p, ctx->forces.p + first, ctx->meta.p + first);
+            BPC_CHECK(cudaEventRecord(ctx->ev_unpacked, ctx->stream));
+            ctx->unpack_recorded = true;
+            BPC_CHECK(cudaEventSynchronize(ctx->ev_h2d));
         } break;
     }
     if (refresh) {
@@ -1074,6 +1093,40 @@ __global__ void k_scatter_forces(uint32_t n, const uint32_t *__restrict__ slots,
         uint32_t m = meta[i].x;
         if ((m & 0xffu) >= MODE_RIGID && !((m >> 8) & (BF_ACTIVE | BF_FROZEN))) meta[i].x = m | (BF_ACTIVE << 8);
     }
+}
+
+// Pipelined read-back: the rows are packed on the main stream into a buffer of their own, the copy to the host runs on a side
+// stream, so the next step's kernels do not wait for the bus (nor the copy for them).
+extern "C" int bpc_bodies_read_begin(bpc_context *ctx, int field, int first, int n, float *out) {
+    if (!ctx) return -1;
+    if (first < 0 || n < 0 || (uint32_t)(first + n) > ctx->n_bodies || (n > 0 && !out)) return fail(ctx, "bpc_bodies_read_begin: range out of bounds");
+    if (field != BPC_FIELD_TRANSFORM && field != BPC_FIELD_LINEAR_VELOCITY && field != BPC_FIELD_ANGULAR_VELOCITY)
+        return fail(ctx, "bpc_bodies_read_begin: field must be TRANSFORM, LINEAR_VELOCITY or ANGULAR_VELOCITY");
+    if (ctx->read_inflight) return fail(ctx, "bpc_bodies_read_begin: the previous read has not been ended (bpc_bodies_read_end)");
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    if (ensure_copy_stream(ctx)) return -1;
+    const int width = field == BPC_FIELD_TRANSFORM ? 12 : 3;
+    ctx->async_staging.reserve((size_t)n * width, false, ctx->stream);
+    if (!ctx->async_staging.p) return fail(ctx, "out of device memory");
+    if (field == BPC_FIELD_TRANSFORM) k_pack_xf<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->xf.p + first, ctx->async_staging.p);
+    else k_pack_vel<<<(n + 255) / 256, 256, 0, ctx->stream>>>((uint32_t)n, ctx->vel.p + first, field == BPC_FIELD_ANGULAR_VELOCITY, ctx->async_staging.p);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaEventRecord(ctx->ev_packed, ctx->stream));
+    BPC_CHECK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_packed, 0));
+    BPC_CHECK(cudaMemcpyAsync(out, ctx->async_staging.p, (size_t)n * width * sizeof(float), cudaMemcpyDeviceToHost, ctx->copy_stream));
+    BPC_CHECK(cudaEventRecord(ctx->ev_read_done, ctx->copy_stream));
+    ctx->read_inflight = true;
+    return 0;
+}
+
+extern "C" int bpc_bodies_read_end(bpc_context *ctx) {
+    if (!ctx) return -1;
+    if (!ctx->read_inflight) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    BPC_CHECK(cudaEventSynchronize(ctx->ev_read_done));
+    ctx->read_inflight = false;
+    return 0;
 }
 
 extern "C" int bpc_bodies_read_slots(bpc_context *ctx, int field, const int32_t *slots, int n, float *out) {

@@ -228,6 +228,15 @@ struct KinState {
 struct bpc_context {
     int device = 0;
     cudaStream_t stream = 0;
+    // pipelined state read-back (bpc_bodies_read_begin / _end): packed on the main stream, copied on a side stream
+    cudaStream_t copy_stream = nullptr, copy_stream_in = nullptr; // device to host / host to device: one must not queue behind the other
+    cudaEvent_t ev_packed = nullptr, ev_read_done = nullptr;
+    bool read_inflight = false;
+    DevBuf<float> async_staging;
+    // bulk force rows go up the same way: copied on the side stream into a buffer of their own, unpacked on the main one
+    cudaEvent_t ev_h2d = nullptr, ev_unpacked = nullptr;
+    bool unpack_recorded = false;
+    DevBuf<float> force_staging;
     std::string err;
 
     // host mirrors of small tables

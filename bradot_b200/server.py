@@ -42,7 +42,7 @@ EXPORTS = [
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
     "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
     "bpc_bodies_set_state", "bpc_bodies_read_slots", "bpc_bodies_write_slots", "bpc_bodies_read_state", "bpc_reserve",
-    "bpc_shape_set_custom_bias", "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_joint_params_write", "bpc_joint_params_read", "bpc_test_segment_math", "bpc_bodies_set_exception",
+    "bpc_shape_set_custom_bias", "bpc_bodies_read_begin", "bpc_bodies_read_end", "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_joint_params_write", "bpc_joint_params_read", "bpc_test_segment_math", "bpc_bodies_set_exception",
     "bpc_bodies_set_max_contacts_reported", "bpc_body_read_contacts", "bpc_contacts_capacity", "bpc_contacts_read",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
     "bpc_space_set_query_exclude", "bpc_space_rest_infos", "bpc_space_cast_motions",
@@ -99,6 +99,8 @@ def load_library(path=LIB_PATH):
     lib.bpc_joints_write.argtypes = [vp, ci, ci, vp]
     lib.bpc_joints_destroy.argtypes = [vp, ci, ci]
     lib.bpc_shape_set_custom_bias.argtypes = [vp, ci, ctypes.c_float]
+    lib.bpc_bodies_read_begin.argtypes = [vp, ci, ci, ci, vp]
+    lib.bpc_bodies_read_end.argtypes = [vp]
     lib.bpc_joint_params_write.argtypes = [vp, ci, ci, ci, vp]
     lib.bpc_joint_params_read.argtypes = [vp, ci, ci, ci, vp]
     lib.bpc_joint_count.argtypes = [vp]
@@ -343,6 +345,15 @@ class PhysicsServerCUDA:
     def joints_write(self, first, records):
         rec = np.ascontiguousarray(records, scenes.JOINT_DT)
         self._check(self.lib.bpc_joints_write(self.ctx, int(first), len(rec), _ptr(rec)))
+
+    def bodies_read_begin(self, field, out, first=0):
+        """Queue a pipelined read of TRANSFORM / a velocity of all bodies from `first` on into `out` (a pinned float32 array);
+        bodies_read_end() waits for it.  The copy overlaps whatever is issued in between, the next step included."""
+        n = out.shape[0]
+        self._check(self.lib.bpc_bodies_read_begin(self.ctx, int(field), int(first), int(n), _ptr(out)))
+
+    def bodies_read_end(self):
+        self._check(self.lib.bpc_bodies_read_end(self.ctx))
 
     def shape_set_custom_bias(self, shape, bias):
         """shape_set_custom_solver_bias: the contact bias of pairs with this shape (0 = the default 0.8)."""

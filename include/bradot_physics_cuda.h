@@ -185,6 +185,12 @@ enum { BPC_STATE_TRANSFORM = 0, BPC_STATE_LINEAR_VELOCITY = 1, BPC_STATE_ANGULAR
 int bpc_bodies_set_state(bpc_context *ctx, int state, const int32_t *slots, int n, const float *values);
 /* Gather / scatter variants of the bulk I/O for a list of bodies (state sync of the active bodies only, forces of the pushed
  * bodies only): one staging copy and one kernel whatever n is. */
+/* The same read, pipelined: _begin queues the read of rows [first, first + n) as they stand after the steps issued so far and
+ * returns; the copy to `out` (pinned host memory, or it will not overlap) runs beside whatever is issued next -- the next
+ * bpc_step included; _end waits until `out` holds the rows.  One read at a time.  TRANSFORM and the two velocities only.
+ * (What flush_queries would use to hand last tick's transforms to the scene while this tick's step runs.) */
+int bpc_bodies_read_begin(bpc_context *ctx, int field, int first, int n, float *out);
+int bpc_bodies_read_end(bpc_context *ctx);
 int bpc_bodies_read_slots(bpc_context *ctx, int field, const int32_t *slots, int n, float *host);
 int bpc_bodies_write_slots(bpc_context *ctx, int field, const int32_t *slots, int n, const float *host);
 /* Transform (12), linear velocity (3), angular velocity (3), active (1) of every body in one call: 19 floats per body. */

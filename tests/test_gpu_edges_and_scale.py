@@ -167,6 +167,41 @@ def test_mixed_pile_is_bit_reproducible_and_every_awake_body_is_stepped():
     b.finish()
 
 
+def test_pipelined_read_back_matches_the_blocking_read():
+    """bpc_bodies_read_begin / _end: the rows queued after step k arrive unchanged although step k + 1 is issued before they are
+    awaited; one read at a time; fields other than the transform and the velocities are refused."""
+    sc = scenes.mixed_pile(5, half=3.5)
+    a, b = server.PhysicsServerCUDA(0), server.PhysicsServerCUDA(0)
+    a.load_scene(sc)
+    b.load_scene(sc)
+    n = len(sc.bodies)
+    import torch
+    bufs = [torch.zeros((n, 12), dtype=torch.float32).pin_memory().numpy() for _ in range(2)]
+    vel = torch.zeros((n, 3), dtype=torch.float32).pin_memory().numpy()
+    expect = []
+    for k in range(12):
+        a.step(sc.dt)
+        expect.append(a.bodies_read(server.FIELD_TRANSFORM).copy())
+    for k in range(12):
+        b.step(sc.dt)
+        b.bodies_read_end()
+        if k:
+            assert np.array_equal(bufs[(k - 1) & 1], expect[k - 1]), k
+        b.bodies_read_begin(server.FIELD_TRANSFORM, bufs[k & 1])
+    with pytest.raises(Exception):
+        b.bodies_read_begin(server.FIELD_TRANSFORM, bufs[0])          # the previous one was not ended
+    b.bodies_read_end()
+    assert np.array_equal(bufs[1], expect[11])
+    b.bodies_read_begin(server.FIELD_LINEAR_VELOCITY, vel)
+    b.bodies_read_end()
+    assert np.array_equal(vel, a.bodies_read(server.FIELD_LINEAR_VELOCITY))
+    with pytest.raises(Exception):
+        b.bodies_read_begin(server.FIELD_ACTIVE, vel)
+    b.bodies_read_end()                                               # nothing in flight: a no-op
+    a.finish()
+    b.finish()
+
+
 def test_edge_cases_of_the_round_2_entry_points():
     """Empty batches, bad handles and refused combinations of the entry points added in round 2 answer with an error message
     (or with nothing), never with a crash or a silent ignore."""
