@@ -628,6 +628,46 @@ def hanging_chains(n_chains=12, chain_len=5, seed=5, cone_twist=False):
     return sc
 
 
+BODY_FURTHER_SHAPE = 0x4000   # scene flag bit14 (harness / engine demo): this record is a further shape of the static body before it
+
+
+def level_geometry(n_side=4, seed=19, merged=True):
+    """A static body with several shapes -- a floor slab, two tilted ramps, a wall, a hull and a sphere bump, the body itself
+    turned and shifted -- under a shower of mixed bodies; a world boundary far below catches what falls off.  In the scene file
+    the further shapes are records of their own flagged BODY_FURTHER_SHAPE (same transform as the body): the harness and the
+    engine demo add them to the body before (body_add_shape), the C ABI sees six static bodies -- which is the same thing to
+    the step (one broadphase entry and one pair object per shape in the reference).  merged=False drops the flag."""
+    sc = Scene(name="level_geometry")
+    rng = np.random.default_rng(seed)
+    xf = IDENT12.copy()
+    th = 0.15
+    xf[0], xf[2], xf[6], xf[8] = np.cos(th), np.sin(th), -np.sin(th), np.cos(th)
+    xf[9], xf[10], xf[11] = 0.5, -0.2, -0.3
+
+    def tilt(angle, axis, pos):
+        f = IDENT12.copy()
+        c, s = np.cos(angle), np.sin(angle)
+        if axis == 0:
+            f[4], f[5], f[7], f[8] = c, -s, s, c
+        else:
+            f[0], f[1], f[3], f[4] = c, -s, s, c
+        f[9:12] = pos
+        return f
+    parts = [(sc.add_shape(SHAPE_BOX, (4.0, 0.2, 4.0)), tilt(0.0, 0, (0, 0, 0))),
+             (sc.add_shape(SHAPE_BOX, (1.5, 0.1, 1.0)), tilt(0.45, 1, (-2.0, 0.8, 1.0))),
+             (sc.add_shape(SHAPE_BOX, (1.0, 0.1, 1.5)), tilt(-0.4, 0, (1.5, 0.7, -1.5))),
+             (sc.add_shape(SHAPE_BOX, (0.15, 1.0, 4.0)), tilt(0.0, 0, (3.9, 1.2, 0))),
+             (sc.add_shape(SHAPE_CONVEX, verts=rng.normal(size=(16, 3)) * np.array([0.7, 0.35, 0.7])), tilt(0.2, 1, (0.5, 0.5, 1.5))),
+             (sc.add_shape(SHAPE_SPHERE, (0.8,)), tilt(0.0, 0, (-1.0, 0.0, -1.5)))]
+    for k, (sh, sxf) in enumerate(parts):
+        sc.add_bodies(1, mode=MODE_STATIC, shape=sh, xf=xf, shape_xf=sxf, friction=0.8, flags=(BODY_FURTHER_SHAPE if (k and merged) else 0))
+    sc.add_static_plane((0, 1, 0), -8.0)
+    g = np.stack(np.meshgrid(np.arange(n_side), np.arange(3), np.arange(n_side), indexing="ij"), -1).reshape(-1, 3)
+    pos = np.stack([(g[:, 0] - (n_side - 1) * 0.5) * 1.3 + 0.4, 2.2 + g[:, 1] * 1.2, (g[:, 2] - (n_side - 1) * 0.5) * 1.3], -1)
+    _mixed_bodies(sc, rng, pos)
+    return sc
+
+
 JOINT_HINGE_SIMPLE = 16   # scene flag (harness / engine demo): make the hinge with joint_make_hinge_simple from the frames' origins and z axes
 
 

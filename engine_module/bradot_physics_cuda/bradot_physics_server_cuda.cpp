@@ -253,6 +253,7 @@ struct BpcExcludeScope {
 			if (slot >= 0) {
 				r_slots.push_back(slot);
 			}
+			p_server->body_part_slots(r, r_slots); // a static body's further shapes
 		}
 		if (!r_slots.is_empty()) {
 			set = bpc_space_set_query_exclude(ctx, r_slots.ptr(), (int)r_slots.size()) == 0;
@@ -297,7 +298,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 		r.rid = is_area ? server->area_of_handle[area_handle]->self : server->body_of_slot[out[i].body]->self;
 		r.collider_id = is_area ? server->area_of_handle[area_handle]->instance_id : server->body_of_slot[out[i].body]->instance_id;
 		r.collider = r.collider_id.is_valid() ? ObjectDB::get_instance(r.collider_id) : nullptr;
-		r.shape = 0;
+		r.shape = is_area ? 0 : server->body_of_slot[out[i].body]->shape_index;
 		r.face_index = -1;
 	}
 	return hits;
@@ -336,7 +337,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_
 		r_results[cc].rid = server->body_of_slot[slots[i]]->self;
 		r_results[cc].collider_id = server->body_of_slot[slots[i]]->instance_id;
 		r_results[cc].collider = r_results[cc].collider_id.is_valid() ? ObjectDB::get_instance(r_results[cc].collider_id) : nullptr;
-		r_results[cc].shape = 0;
+		r_results[cc].shape = server->body_of_slot[slots[i]]->shape_index;
 		cc++;
 	}
 	return cc;
@@ -371,7 +372,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_
 			r_results[cc].rid = server->body_of_slot[slots[i]]->self;
 			r_results[cc].collider_id = server->body_of_slot[slots[i]]->instance_id;
 			r_results[cc].collider = r_results[cc].collider_id.is_valid() ? ObjectDB::get_instance(r_results[cc].collider_id) : nullptr;
-			r_results[cc].shape = 0;
+			r_results[cc].shape = server->body_of_slot[slots[i]]->shape_index;
 		}
 		cc++;
 	}
@@ -414,7 +415,7 @@ void BradotPhysicsDirectSpaceStateCUDA::_fill_rest_info(const bpc_rest_info &p_i
 	r_info->linear_velocity = Vector3(p_info.linear_velocity[0], p_info.linear_velocity[1], p_info.linear_velocity[2]);
 	r_info->rid = b ? b->self : RID();
 	r_info->collider_id = b ? b->instance_id : ObjectID();
-	r_info->shape = 0;
+	r_info->shape = b ? b->shape_index : 0;
 }
 
 bool BradotPhysicsDirectSpaceStateCUDA::cast_motion(const ShapeParameters &p_parameters, real_t &p_closest_safe, real_t &p_closest_unsafe, ShapeRestInfo *r_info) {
@@ -532,17 +533,17 @@ RID BradotPhysicsServerCUDA::body_create() {
 }
 
 void BradotPhysicsServerCUDA::_fill_desc(const Body *p_body, bpc_body_desc &r_desc) {
-	const Body *b = p_body;
+	const Body *b = p_body->parent ? p_body->parent : p_body; // a further shape of a static body: the body's own values ...
 	r_desc = {};
 	const Space *space = space_owner.get_or_null(b->space);
-	Shape *shape = shape_owner.get_or_null(b->shape);
+	Shape *shape = shape_owner.get_or_null(p_body->shape); // ... but this record's shape
 	r_desc.space = space ? space->handle : 0;
 	r_desc.mode = (uint32_t)b->mode;
 	r_desc.shape = shape ? _shape_handle(shape) : 0;
 	r_desc.flags = (b->can_sleep ? 1 : 0) | (b->ccd ? 2 : 0) | (b->lin_damp_replace ? 16 : 0) | (b->ang_damp_replace ? 32 : 0) |
 			(b->omit_force_integration ? 64 : 0) | (b->ray_pickable ? 0 : 128) | ((b->locked_axis & 63) << 8);
 	_xf_to_floats(b->xf, r_desc.xf);
-	_xf_to_floats(b->shape_xf, r_desc.shape_xf);
+	_xf_to_floats(p_body->shape_xf, r_desc.shape_xf);
 	r_desc.linvel[0] = b->linvel.x; r_desc.linvel[1] = b->linvel.y; r_desc.linvel[2] = b->linvel.z;
 	r_desc.angvel[0] = b->angvel.x; r_desc.angvel[1] = b->angvel.y; r_desc.angvel[2] = b->angvel.z;
 	r_desc.mass = b->mass; r_desc.friction = b->friction; r_desc.bounce = b->bounce; r_desc.gravity_scale = b->gravity_scale;
@@ -557,9 +558,28 @@ void BradotPhysicsServerCUDA::_body_changed(Body *p_body) {
 		p_body->dirty = true;
 		dirty_bodies.push_back(p_body);
 	}
+	for (Body *part : p_body->parts) {
+		_body_changed(part);
+	}
+}
+
+// the record that holds shape `p_shape_idx` of a body: the body itself for 0, one of its parts beyond
+BradotPhysicsServerCUDA::Body *BradotPhysicsServerCUDA::_body_shape_record(Body *p_body, int p_shape_idx) const {
+	if (p_shape_idx == 0) {
+		return p_body->shape.is_valid() ? p_body : nullptr;
+	}
+	return (p_shape_idx > 0 && (uint32_t)p_shape_idx <= p_body->parts.size()) ? p_body->parts[p_shape_idx - 1] : nullptr;
+}
+
+void BradotPhysicsServerCUDA::_body_drop_part(Body *p_part) {
+	_body_leave_space(p_part);
+	memdelete(p_part);
 }
 
 void BradotPhysicsServerCUDA::_body_leave_space(Body *p_body) {
+	for (Body *part : p_body->parts) {
+		_body_leave_space(part);
+	}
 	if (p_body->pending) {
 		pending_bodies.erase(p_body);
 		p_body->pending = false;
@@ -618,6 +638,13 @@ void BradotPhysicsServerCUDA::body_set_space(RID p_body, RID p_space) {
 		body->pending = true;
 		pending_bodies.push_back(body);
 	}
+	for (Body *part : body->parts) {
+		part->space = p_space;
+		if (p_space.is_valid() && !part->pending) {
+			part->pending = true;
+			pending_bodies.push_back(part);
+		}
+	}
 }
 
 RID BradotPhysicsServerCUDA::body_get_space(RID p_body) const {
@@ -632,6 +659,7 @@ void BradotPhysicsServerCUDA::body_set_mode(RID p_body, BodyMode p_mode) {
 	if (body->mode == p_mode) {
 		return;
 	}
+	ERR_FAIL_COND_MSG(!body->parts.is_empty() && p_mode != BODY_MODE_STATIC, "BradotPhysicsCUDA: only static bodies can have several shapes in this version.");
 	body->mode = p_mode;
 	_body_changed(body);
 }
@@ -646,8 +674,24 @@ void BradotPhysicsServerCUDA::body_add_shape(RID p_body, RID p_shape, const Tran
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
 	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
-	ERR_FAIL_COND_MSG(body->shape.is_valid(), "BradotPhysicsCUDA: one shape per body in this version.");
 	ERR_FAIL_COND_MSG(p_disabled, "BradotPhysicsCUDA: disabled shapes are not supported yet.");
+	if (body->shape.is_valid()) { // a further shape: static bodies only, as a record of its own
+		ERR_FAIL_COND_MSG(body->mode != BODY_MODE_STATIC, "BradotPhysicsCUDA: only static bodies can have several shapes in this version.");
+		Body *part = memnew(Body);
+		part->parent = body;
+		part->self = body->self;
+		part->instance_id = body->instance_id;
+		part->space = body->space;
+		part->shape = p_shape;
+		part->shape_xf = p_transform;
+		part->shape_index = body->parts.size() + 1;
+		body->parts.push_back(part);
+		if (body->space.is_valid()) {
+			part->pending = true;
+			pending_bodies.push_back(part);
+		}
+		return;
+	}
 	body->shape = p_shape;
 	body->shape_xf = p_transform;
 	_body_changed(body);
@@ -657,39 +701,56 @@ void BradotPhysicsServerCUDA::body_set_shape(RID p_body, int p_shape_idx, RID p_
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
 	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
-	ERR_FAIL_COND(p_shape_idx != 0 || !body->shape.is_valid());
-	body->shape = p_shape;
-	_body_changed(body);
+	Body *rec = _body_shape_record(body, p_shape_idx);
+	ERR_FAIL_NULL(rec);
+	rec->shape = p_shape;
+	_body_changed(rec);
 }
 
 void BradotPhysicsServerCUDA::body_set_shape_transform(RID p_body, int p_shape_idx, const Transform3D &p_transform) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
-	ERR_FAIL_COND(p_shape_idx != 0 || !body->shape.is_valid());
-	body->shape_xf = p_transform;
-	_body_changed(body);
+	Body *rec = _body_shape_record(body, p_shape_idx);
+	ERR_FAIL_NULL(rec);
+	rec->shape_xf = p_transform;
+	_body_changed(rec);
 }
 
 RID BradotPhysicsServerCUDA::body_get_shape(RID p_body, int p_shape_idx) const {
 	const Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL_V(body, RID());
-	ERR_FAIL_COND_V(p_shape_idx != 0 || !body->shape.is_valid(), RID());
-	return body->shape;
+	const Body *rec = _body_shape_record(const_cast<Body *>(body), p_shape_idx);
+	ERR_FAIL_NULL_V(rec, RID());
+	return rec->shape;
 }
 
 Transform3D BradotPhysicsServerCUDA::body_get_shape_transform(RID p_body, int p_shape_idx) const {
 	const Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL_V(body, Transform3D());
-	ERR_FAIL_COND_V(p_shape_idx != 0 || !body->shape.is_valid(), Transform3D());
-	return body->shape_xf;
+	const Body *rec = _body_shape_record(const_cast<Body *>(body), p_shape_idx);
+	ERR_FAIL_NULL_V(rec, Transform3D());
+	return rec->shape_xf;
 }
 
 // A body without its shape takes no part in the step: it leaves the GPU side until it is given a shape again.
 void BradotPhysicsServerCUDA::body_remove_shape(RID p_body, int p_shape_idx) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
-	ERR_FAIL_COND(p_shape_idx != 0 || !body->shape.is_valid());
-	body_clear_shapes(p_body);
+	ERR_FAIL_NULL(_body_shape_record(body, p_shape_idx));
+	if (body->parts.is_empty()) {
+		body_clear_shapes(p_body);
+		return;
+	}
+	// the shapes behind it move down one index (bradot_collision_object_3d.cpp:98-115): shift them through the records
+	// and drop the last one
+	for (int i = p_shape_idx; i < (int)body->parts.size(); i++) {
+		Body *dst = _body_shape_record(body, i), *src = body->parts[i];
+		dst->shape = src->shape;
+		dst->shape_xf = src->shape_xf;
+		_body_changed(dst);
+	}
+	_body_drop_part(body->parts[body->parts.size() - 1]);
+	body->parts.resize(body->parts.size() - 1);
 }
 
 void BradotPhysicsServerCUDA::body_clear_shapes(RID p_body) {
@@ -698,6 +759,10 @@ void BradotPhysicsServerCUDA::body_clear_shapes(RID p_body) {
 	if (!body->shape.is_valid()) {
 		return;
 	}
+	for (Body *part : body->parts) {
+		_body_drop_part(part);
+	}
+	body->parts.clear();
 	bool in_space = body->slot >= 0 || body->pending;
 	_body_leave_space(body);
 	body->shape = RID();
@@ -710,13 +775,16 @@ void BradotPhysicsServerCUDA::body_clear_shapes(RID p_body) {
 int BradotPhysicsServerCUDA::body_get_shape_count(RID p_body) const {
 	const Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL_V(body, -1);
-	return body->shape.is_valid() ? 1 : 0;
+	return body->shape.is_valid() ? 1 + (int)body->parts.size() : 0;
 }
 
 void BradotPhysicsServerCUDA::body_attach_object_instance_id(RID p_body, ObjectID p_id) {
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
 	body->instance_id = p_id; // host-side only: query results are mapped back through body_of_slot
+	for (Body *part : body->parts) {
+		part->instance_id = p_id;
+	}
 }
 
 ObjectID BradotPhysicsServerCUDA::body_get_object_instance_id(RID p_body) const {
@@ -828,6 +896,12 @@ void BradotPhysicsServerCUDA::body_set_state(RID p_body, BodyState p_state, cons
 	}
 	int32_t slot = body->slot;
 	ERR_FAIL_COND_MSG(bpc_bodies_set_state(ctx, (int)p_state, &slot, 1, f) < 0, bpc_last_error(ctx));
+	for (Body *part : body->parts) { // the further shapes of a static body are placed with it
+		if (part->slot >= 0 && p_state == BODY_STATE_TRANSFORM) {
+			int32_t ps = part->slot;
+			ERR_FAIL_COND_MSG(bpc_bodies_set_state(ctx, (int)p_state, &ps, 1, f) < 0, bpc_last_error(ctx));
+		}
+	}
 	// keep the read-back copy in step with what was just set (a callback may set and then get)
 	float *st = state_cache_valid && (uint32_t)(slot + 1) * 19 <= state_cache.size() ? &state_cache[slot * 19] : nullptr;
 	if (st) {
@@ -1255,6 +1329,7 @@ bool BradotPhysicsServerCUDA::body_test_motion(RID p_body, const MotionParameter
 		if (s >= 0) {
 			excluded.push_back(s);
 		}
+		body_part_slots(r, excluded);
 	}
 	if (!p_parameters.exclude_objects.is_empty()) {
 		for (uint32_t s = 0; s < body_of_slot.size(); s++) {
@@ -1297,9 +1372,9 @@ bool BradotPhysicsServerCUDA::body_test_motion(RID p_body, const MotionParameter
 			o.collider_velocity = Vector3(c.collider_velocity[0], c.collider_velocity[1], c.collider_velocity[2]);
 			o.collider_angular_velocity = Vector3(c.collider_angular_velocity[0], c.collider_angular_velocity[1], c.collider_angular_velocity[2]);
 			o.depth = c.depth;
-			o.local_shape = 0;
-			o.collider_shape = 0;
 			Body *other = (c.collider >= 0 && (uint32_t)c.collider < body_of_slot.size()) ? body_of_slot[c.collider] : nullptr;
+			o.local_shape = 0;
+			o.collider_shape = other ? other->shape_index : 0;
 			o.collider = other ? other->self : RID();
 			o.collider_id = other ? other->instance_id : ObjectID();
 		}
@@ -2323,6 +2398,10 @@ void BradotPhysicsServerCUDA::free(RID p_rid) {
 		Body *b = body_owner.get_or_null(p_rid);
 		reporting_bodies -= b->max_contacts_reported > 0 ? 1 : 0;
 		_body_leave_space(b);
+		for (Body *part : b->parts) {
+			memdelete(part);
+		}
+		b->parts.clear();
 		if (b->pushed) {
 			pushed_bodies.erase(b);
 		}

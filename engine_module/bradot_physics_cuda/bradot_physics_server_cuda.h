@@ -149,6 +149,12 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		Variant fi_udata;
 		BradotPhysicsDirectBodyStateCUDA *direct_state = nullptr;
 		LocalVector<RID> exceptions;
+		// several shapes: a STATIC body's further shapes are bodies of their own on the GPU side (exactly what the reference's
+		// step sees: one broadphase entry and one pair object per shape, P3D/bradot_collision_object_3d.cpp:156-184,
+		// P3D/bradot_body_pair_3d.cpp) -- hidden records that take everything but shape and shape transform from `parent`
+		Body *parent = nullptr;
+		int shape_index = 0;
+		LocalVector<Body *> parts;
 		int slot = -1; // bpc body index once uploaded
 	};
 	struct Joint {
@@ -239,6 +245,8 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	void _fill_desc(const Body *p_body, bpc_body_desc &r_desc);
 	void _fill_joint_desc(const Joint *p_joint, bpc_joint_desc &r_desc);
 	void _body_changed(Body *p_body);
+	Body *_body_shape_record(Body *p_body, int p_shape_idx) const;
+	void _body_drop_part(Body *p_part);
 	void _joint_changed(Joint *p_joint);
 	void _body_leave_space(Body *p_body);
 	void _body_update_callback_list(Body *p_body);
@@ -251,6 +259,16 @@ public:
 	int32_t body_slot_of(const RID &p_rid) const {
 		const Body *b = body_owner.get_or_null(p_rid);
 		return b ? b->slot : -1;
+	}
+	void body_part_slots(const RID &p_rid, LocalVector<int32_t> &r_slots) const { // the slots of a static body's further shapes
+		const Body *b = body_owner.get_or_null(p_rid);
+		if (b) {
+			for (const Body *part : b->parts) {
+				if (part->slot >= 0) {
+					r_slots.push_back(part->slot);
+				}
+			}
+		}
 	}
 
 private:

@@ -224,6 +224,11 @@ int main(int argc, char **argv) {
 		shape_r.push_back(sh);
 	}
 	for (const ScnBody &b : bodies) {
+		if ((b.flags & 0x4000) && !body_r.empty()) { // bit14: a further shape of the (static) body before it
+			ps->body_add_shape(body_r.back(), shape_r[b.shape], xf_from(b.shape_xf), false);
+			body_r.push_back(body_r.back());
+			continue;
+		}
 		RID body = ps->body_create();
 		ps->body_set_mode(body, (PhysicsServer3D::BodyMode)b.mode);
 		ps->body_add_shape(body, shape_r[b.shape], xf_from(b.shape_xf), false);

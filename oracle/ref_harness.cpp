@@ -195,6 +195,7 @@ struct World {
 	std::vector<Vector3> kin_lin;
 	std::vector<float> kin_wy;
 	std::vector<uint32_t> body_flags;
+	std::vector<int> body_shape; // which shape of its body a scene record stands for (0; 1.. for the further shapes of a static body)
 	std::vector<char> body_freed;
 	// sweep order of the last step, recorded space by space: (island counted over all spaces, constraint)
 	std::vector<std::pair<int, const BradotConstraint3D *>> last_order;
@@ -266,8 +267,8 @@ static void dump_step(Dump &d, World &w, int step) {
 		put3(bs, b->get_angular_velocity());
 		bs.push_back(b->is_active() ? 1.0f : 0.0f);
 		bs.push_back(b->still_time);
-		// broadphase item (shape 0)
-		const BradotCollisionObject3D::Shape &s = b->shapes[0];
+		// broadphase item of the shape this record stands for
+		const BradotCollisionObject3D::Shape &s = b->shapes[w.body_shape[i]];
 		put3(items, s.aabb_cache.position);
 		put3(items, s.aabb_cache.size);
 		BradotSpace3D *space = b->get_space();
@@ -327,14 +328,17 @@ static void dump_step(Dump &d, World &w, int step) {
 			continue;
 		}
 		BradotBody3D *b = w.body_ptr[i];
+		if (w.body_shape[i] != 0) {
+			continue; // a further shape of the body before it: its pairs were listed there
+		}
 		for (const KeyValue<BradotConstraint3D *, int> &E : b->get_constraint_map()) {
 			BradotBodyPair3D *p = dynamic_cast<BradotBodyPair3D *>(E.key);
 			if (!p || p->A != b) {
 				continue;
 			}
 			pair_index[p] = pi.size() / 4;
-			pi.push_back(w.body_index[p->A]);
-			pi.push_back(w.body_index[p->B]);
+			pi.push_back(w.body_index[p->A] + p->shape_A); // (the further shapes of a static body follow it in the scene)
+			pi.push_back(w.body_index[p->B] + p->shape_B);
 			pi.push_back(p->contact_count);
 			pi.push_back((p->collided ? 1 : 0) | (p->collide_A ? 2 : 0) | (p->collide_B ? 4 : 0) | (p->check_ccd ? 8 : 0));
 			put3(pf, p->sep_axis);
@@ -1018,9 +1022,22 @@ int main(int argc, char **argv) {
 	}
 	for (uint32_t i = 0; i < hd.n_bodies; i++) {
 		const ScnBody &b = sbodies[i];
+		if ((b.flags & 0x4000) && i > 0) { // bit14: a further shape of the (static) body before it, not a body of its own
+			RID prev = w.bodies[i - 1]; // (its shape was added when the body was made, before it entered the space: see below)
+			w.bodies.push_back(prev);
+			w.body_ptr.push_back(w.body_ptr[i - 1]);
+			w.body_shape.push_back(w.body_shape[i - 1] + 1);
+			w.body_space.push_back(b.space);
+			w.body_flags.push_back(b.flags);
+			w.body_freed.push_back(0);
+			continue;
+		}
 		RID body = ps->body_create();
 		ps->body_set_mode(body, (PhysicsServer3D::BodyMode)b.mode);
 		ps->body_add_shape(body, w.shapes[b.shape], xf_from(b.shape_xf), false);
+		for (uint32_t j = i + 1; j < hd.n_bodies && (sbodies[j].flags & 0x4000); j++) { // its further shapes, in order
+			ps->body_add_shape(body, w.shapes[sbodies[j].shape], xf_from(sbodies[j].shape_xf), false);
+		}
 		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_MASS, b.mass);
 		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_FRICTION, b.friction);
 		ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_BOUNCE, b.bounce);
@@ -1064,6 +1081,7 @@ int main(int argc, char **argv) {
 		BradotBody3D *bp = ps->body_owner.get_or_null(body);
 		w.body_ptr.push_back(bp);
 		w.body_index[bp] = i;
+		w.body_shape.push_back(0);
 		w.body_space.push_back(b.space);
 		w.body_flags.push_back(b.flags);
 		w.body_freed.push_back(0);

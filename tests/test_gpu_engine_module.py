@@ -115,6 +115,39 @@ def test_engine_module_forces_and_ccd_match_direct_c_abi(tmp_path, name):
         assert np.all(direct[ccd, 2] < 3.0)        # stopped by the wall / the plates
 
 
+def test_engine_module_static_body_with_several_shapes(tmp_path):
+    """body_add_shape beyond the first on a static body (level geometry): the module keeps the further shapes as records of their
+    own on the GPU side.  Against (1) the C ABI stepping the same scene with six static bodies: the same to rounding; (2) the reference with
+    ONE static body of six shapes, teacher-forced (its pairs are per shape: the same pair list, contacts 1e-5, state 1e-4)."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    if not parity.have_oracle():
+        pytest.skip("oracle/_ref/oracle_step not built")
+    sc = scenes.level_geometry()
+    steps = 50
+    path = str(tmp_path / "scene.bscn")
+    sc.write(path)
+    r = subprocess.run([DEMO, path, str(steps)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    engine = np.array(out["origins"], np.float32)
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc)
+    for _ in range(steps):
+        ps.step(sc.dt)
+    direct = ps.bodies_read(server.FIELD_TRANSFORM)[:, 9:12]
+    st = ps.stats()
+    ps.finish()
+    # (the hull is built by the engine's ConvexHullComputer there and by bradot_b200.hull here: same hull, another face order)
+    assert np.max(np.abs(engine - direct)) < 5e-3, float(np.abs(engine - direct).max())
+    assert out["collision_pairs"] == st["collision_pairs"] and st["contact_pairs"] > 10
+    # the reference steps ONE static body of six shapes; its pairs are listed per shape, which is what the six records are
+    w = parity.teacher_forced(sc, 60, [1, 15, 30, 45, 58])
+    assert w["state"] < 1e-4 and w["contact"] < 1e-5 and w["contacts"] > 50, w
+    dyn = sc.bodies["mode"] == scenes.MODE_RIGID
+    assert np.mean(direct[dyn, 1] > -1.0) > 0.6            # most of them came to lie on the level, not on the plane below
+
+
 def test_engine_module_simple_hinges_match_the_reference(tmp_path):
     """joint_make_hinge_simple through the module (the frames built from pivots, axes and body A's transform, as
     joints/bradot_hinge_joint_3d.cpp:69-108 does) against the reference making the same hinges: free-running, positions to 2 mm."""
