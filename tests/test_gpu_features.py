@@ -2,6 +2,8 @@
 and body damp modes (a2, a7), per-space solver iterations (a16), body_set_state and free() at run time (boundary),
 inactive spaces, and the reference's own helper vectors (tests/core/math/test_geometry_3d.h).  The checker is the
 reference's own code (oracle/_ref/oracle_step)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -421,6 +423,34 @@ def test_height_maps_match_the_reference():
     w = parity.teacher_forced(sc, 151, [20, 45, 70, 100, 150])
     assert w["colliding"] > 20 and w["contacts"] > 40, w
     assert w["contact"] < CONTACT_TOL and w["state"] < 1e-4, w
+
+
+@pytest.mark.parametrize("name", ["cone_twist", "slider", "sixdof", "chains", "pile"])
+def test_solver_bins_and_grid_barrier_path_agree(name):
+    """The teacher-forced tests run the grid-barrier solver (a forced order does).  Left to itself a scene of small islands goes
+    through the solver bins, where contacts and joints work on bodies held in shared memory (solve_pair<true>, solve_joint<true>,
+    solve_joint_ext<true>).  Both paths sweep the same colours, so free-running they must agree bit for bit: the same scene
+    stepped by a context with the bins and by one without (BPC_NO_BINS=1, read when the context is made)."""
+    sc = {"cone_twist": lambda: scenes.hanging_chains(cone_twist=True), "slider": scenes.slider_rigs, "sixdof": scenes.sixdof_rigs,
+          "chains": scenes.hanging_chains, "pile": lambda: scenes.batched_worlds(6, lattice=(4, 3, 4))}[name]()
+    steps = 40
+    states, on_barrier = [], []
+    for no_bins in ("0", "1"):
+        os.environ["BPC_NO_BINS"] = no_bins
+        try:
+            ps = server.PhysicsServerCUDA(0)
+        finally:
+            os.environ.pop("BPC_NO_BINS", None)
+        ps.load_scene(sc)
+        for _ in range(steps):
+            ps.step(sc.dt)
+        states.append(ps.bodies_read_state())
+        on_barrier.append(ps.stats()["barrier_constraints"])
+        ps.finish()
+    assert on_barrier[0] < on_barrier[1], on_barrier        # the bins did take constraints off the grid-barrier path
+    assert np.isfinite(states[0]).all()
+    assert np.abs(states[0][:, 9:12] - sc.bodies["xf"][:, 9:12]).max() > 0.2
+    assert np.array_equal(states[0], states[1]), float(np.abs(states[0] - states[1]).max())
 
 
 def test_shape_custom_solver_bias_matches_the_reference():
