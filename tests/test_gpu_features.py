@@ -453,6 +453,24 @@ def test_solver_bins_and_grid_barrier_path_agree(name):
     assert np.array_equal(states[0], states[1]), float(np.abs(states[0] - states[1]).max())
 
 
+@pytest.mark.parametrize("name", ["cone_twist", "slider", "sixdof"])
+def test_new_joint_types_in_islands_with_contacts(name):
+    """The rigs of the joint tests above, now colliding: a floor under them that the lower boxes land on and neighbours that touch,
+    so that islands hold joints AND contacts (the reference sweeps them in one list, joints by solver priority).  Teacher-forced:
+    same pair list, contacts 1e-5, state 1e-4."""
+    _need_oracle()
+    sc = {"cone_twist": lambda: scenes.hanging_chains(6, 4, cone_twist=True), "slider": lambda: scenes.slider_rigs(8), "sixdof": lambda: scenes.sixdof_rigs(8)}[name]()
+    dyn = sc.bodies["mode"] == scenes.MODE_RIGID
+    sc.bodies["layer"][dyn] = 1
+    sc.bodies["mask"][dyn] = 1
+    sc.joints["priority"] = 0      # (an island with contacts and priority-2 joints loses its contacts from the harness's record of the order)
+    lowest = float(sc.bodies["xf"][dyn, 10].min())
+    sc.add_static_plane((0, 1, 0), lowest - (0.1 if name == "cone_twist" else 0.35))      # (the chains hang: their last link starts in the floor)
+    _, dump = parity.run_oracle(sc, 70)
+    w = parity.teacher_forced(sc, 70, [1, 10, 20, 35, 50, 68], dump=dump)
+    assert w["state"] < STATE_TOL and w["contact"] < CONTACT_TOL and w["contacts"] > 20, w
+
+
 def test_shape_custom_solver_bias_matches_the_reference():
     """shape_set_custom_solver_bias (BradotBodyPair3D::setup, bradot_body_pair_3d.cpp:344-357): a pair takes the bias of the shape
     that has one, or the mean of both, in place of 0.8.  A settling mixed pile where the spheres, the boxes and the floor
