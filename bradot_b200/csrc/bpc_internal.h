@@ -150,6 +150,7 @@ struct AreaRec {
 #define BIN_BLOCK 256u
 #define BIN_MAX_BODIES 704u
 #define BIN_MAX_CONS 2048u
+#endif
 
 // The exclude list of the space queries (ShapeParameters::exclude and friends, bradot_space_3d.cpp:86,151,233,294,408,540):
 // sorted body indices, looked up per candidate.
@@ -167,8 +168,6 @@ __device__ __forceinline__ bool q_excluded(const QExclude &e, uint32_t body) {
     }
     return lo < e.n && e.ids[lo] == body;
 }
-#endif
-
 #endif
 
 // stages timed by bpc_set_profiling: forces, broadphase, islands, narrowphase, schedule, solve, integrate+sleep

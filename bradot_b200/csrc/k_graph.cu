@@ -17,6 +17,9 @@ namespace cg = cooperative_groups;
 #define MAX_COLORS 64
 #define BIN_COLS (MAX_COLORS + 1) // colours 0..63 and the overflow group
 #define BIN_KEYS (BIN_COLS * 4)  // (colour, work class) runs of the barrier path
+#ifndef BINS_PER_COLOUR_LIMIT
+#define BINS_PER_COLOUR_LIMIT 384u // constraints per colour and SM below which the bins take over (measured, see bpc_launch_schedule)
+#endif
 static inline uint32_t nblk(uint32_t n, uint32_t t) { return (n + t - 1) / t; }
 
 __global__ void __launch_bounds__(GR_THREADS) k_cc_init(uint32_t n, uint32_t *__restrict__ label, uint32_t *__restrict__ flag) {
@@ -541,7 +544,7 @@ int bpc_launch_schedule(bpc_context *ctx) {
     bool wanted = ctx->use_bins;
     if (wanted && ctx->h_counters[CNT_COLORS]) {
         uint64_t per_colour = (uint64_t)(ctx->h_counters[CNT_CONS] + nj) / ctx->h_counters[CNT_COLORS];
-        wanted = per_colour < (uint64_t)ctx->sm_count * 384u;
+        wanted = per_colour < (uint64_t)ctx->sm_count * BINS_PER_COLOUR_LIMIT;
     }
     const bool bins = wanted && ctx->h_ccd_ids.empty();
     ctx->n_bins = bins ? n_bins : 0;
