@@ -79,7 +79,7 @@ static float shape_volume(const ShapeRec &s) {
     }
 }
 
-static void mass_properties(const ShapeRec &sh, const bpc_body_desc &d, BodyProps &p, float &inv_mass) {
+static void mass_properties(const ShapeRec &sh, const bpc_body_desc &d, BodyProps &p, float &inv_mass, const bpc_context::MassOverride *ov = nullptr) {
     p.com_mass = make_float4(0.f, 0.f, 0.f, d.mass);
     p.iinv_gs = make_float4(0.f, 0.f, 0.f, d.gravity_scale);
     p.a0 = make_float4(1.f, 0.f, 0.f, d.lin_damp);
@@ -99,6 +99,7 @@ static void mass_properties(const ShapeRec &sh, const bpc_body_desc &d, BodyProp
             com += mass_new * so;
             com /= d.mass;
         }
+        if (ov && ov->has_com) com = V3(ov->com[0], ov->com[1], ov->com[2]); // calculate_center_of_mass = false
         M3 tensor = m3_zero();
         bool inertia_set = false;
         if (area != 0.0f && std::isfinite(area)) {
@@ -117,7 +118,17 @@ static void mass_properties(const ShapeRec &sh, const bpc_body_desc &d, BodyProp
             }
         }
         if (!inertia_set) tensor = M3();
-        M3 axes = transposed(diagonalize(tensor));
+        M3 axes;
+        if (ov && ov->has_inertia && !ov->partial && ov->inertia[0] > 0.f && ov->inertia[1] > 0.f && ov->inertia[2] > 0.f) {
+            // calculate_inertia = false: the given values about the body's own axes (bradot_body_3d.cpp:216-222)
+            tensor = M3(V3(ov->inertia[0], 0.f, 0.f), V3(0.f, ov->inertia[1], 0.f), V3(0.f, 0.f, ov->inertia[2]));
+        } else {
+            if (ov && ov->has_inertia) { // partial custom inertia (:130-139)
+                for (int k = 0; k < 3; k++)
+                    if (ov->inertia[k] > 0.f) tensor.r[k][k] = ov->inertia[k];
+            }
+            axes = transposed(diagonalize(tensor));
+        }
         p.com_mass = make_float4(com.x, com.y, com.z, d.mass);
         p.iinv_gs = make_float4(1.0f / tensor.r[0][0], 1.0f / tensor.r[1][1], 1.0f / tensor.r[2][2], d.gravity_scale);
         p.a0 = make_float4(axes.r[0].x, axes.r[0].y, axes.r[0].z, d.lin_damp);
@@ -255,7 +266,8 @@ static int write_body_slots(bpc_context *ctx, const uint32_t *slots, const bpc_b
         vel[i].ang = make_float4(d.angvel[0], d.angvel[1], d.angvel[2], 0.f);
         memset(&props[i], 0, sizeof(BodyProps));
         float inv_mass;
-        mass_properties(sh, d, props[i], inv_mass);
+        auto ovi = ctx->h_mass_override.find(slot);
+        mass_properties(sh, d, props[i], inv_mass, ovi == ctx->h_mass_override.end() ? nullptr : &ovi->second);
         memset(&mw[i], 0, sizeof(BodyMassW));
         mw[i].m = make_float4(inv_mass, d.friction, d.bounce, 0.f);
         uint32_t flags = (d.flags & 1u ? BF_CAN_SLEEP : 0u) | (d.flags & 4u ? 0u : BF_ACTIVE) | (d.flags & 2u ? BF_CCD : 0u) |
@@ -512,6 +524,7 @@ extern "C" int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n)
             ctx->report_dirty = true;
         }
         ctx->h_dead[i] = 1;
+        ctx->h_mass_override.erase(i);
         ctx->h_mode[i] = MODE_STATIC;
         ctx->h_big[i] = 0;
         ctx->h_ccd[i] = 0;
@@ -1097,6 +1110,39 @@ __global__ void k_scatter_forces(uint32_t n, const uint32_t *__restrict__ slots,
 
 // Pipelined read-back: the rows are packed on the main stream into a buffer of their own, the copy to the host runs on a side
 // stream, so the next step's kernels do not wait for the bus (nor the copy for them).
+extern "C" int bpc_bodies_set_mass_override(bpc_context *ctx, const int32_t *slots, int n, const float *inertia, const float *center_of_mass) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && !slots)) return fail(ctx, "bpc_bodies_set_mass_override: bad arguments");
+    for (int i = 0; i < n; i++) {
+        if (slots[i] < 0 || (uint32_t)slots[i] >= ctx->n_bodies || ctx->h_dead[slots[i]]) return fail(ctx, "bpc_bodies_set_mass_override: invalid body");
+    }
+    for (int i = 0; i < n; i++) {
+        uint32_t s = (uint32_t)slots[i];
+        if (!inertia && !center_of_mass) {
+            // body_reset_mass_properties (bradot_body_3d.cpp:168-172) sets both "calculate" flags but keeps the inertia vector,
+            // whose positive components go on replacing the diagonal of the computed tensor (:130-139)
+            auto it = ctx->h_mass_override.find(s);
+            if (it != ctx->h_mass_override.end()) {
+                it->second.has_com = false;
+                it->second.partial = true;
+                if (!it->second.has_inertia) ctx->h_mass_override.erase(it);
+            }
+            continue;
+        }
+        bpc_context::MassOverride &o = ctx->h_mass_override[s]; // value-initialised when new
+        if (inertia) {
+            memcpy(o.inertia, inertia + 3 * i, sizeof(o.inertia));
+            o.has_inertia = true;
+            o.partial = false;
+        }
+        if (center_of_mass) {
+            memcpy(o.com, center_of_mass + 3 * i, sizeof(o.com));
+            o.has_com = true;
+        }
+    }
+    return 0;
+}
+
 extern "C" int bpc_bodies_read_begin(bpc_context *ctx, int field, int first, int n, float *out) {
     if (!ctx) return -1;
     if (first < 0 || n < 0 || (uint32_t)(first + n) > ctx->n_bodies || (n > 0 && !out)) return fail(ctx, "bpc_bodies_read_begin: range out of bounds");

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "bpc_math.cuh"
@@ -247,6 +248,8 @@ struct bpc_context {
     std::vector<uint32_t> h_mindex; // per face: [count, idx...] packed; face_ofs indexes h_mfaces
     std::vector<uint2> h_mfaces;    // (index_ofs, count)
     std::vector<JointRec> h_joints;
+    struct MassOverride { float inertia[3]; float com[3]; bool has_inertia, has_com, partial; }; // partial: after a reset (see bpc_bodies_set_mass_override)
+    std::unordered_map<uint32_t, MassOverride> h_mass_override; // body_set_param(INERTIA / CENTER_OF_MASS), by slot
     std::vector<float> h_shape_bias; // shape_set_custom_solver_bias per shape; empty until one is set
     DevBuf<float> d_shape_bias;
     std::vector<float> h_jext; // JEXT_STRIDE values per joint, present once a joint with a long parameter table exists

@@ -832,11 +832,44 @@ void BradotPhysicsServerCUDA::body_set_param(RID p_body, BodyParameter p_param, 
 		case BODY_PARAM_ANGULAR_DAMP: body->ang_damp = p_value; break;
 		case BODY_PARAM_LINEAR_DAMP_MODE: body->lin_damp_replace = (int)p_value == BODY_DAMP_MODE_REPLACE; break;
 		case BODY_PARAM_ANGULAR_DAMP_MODE: body->ang_damp_replace = (int)p_value == BODY_DAMP_MODE_REPLACE; break;
+		case BODY_PARAM_INERTIA:
+			body->custom_inertia = p_value;
+			body->has_custom_inertia = true;
+			body->mass_override_dirty = true;
+			break;
+		case BODY_PARAM_CENTER_OF_MASS:
+			body->custom_com = p_value;
+			body->has_custom_com = true;
+			body->mass_override_dirty = true;
+			break;
 		default:
-			BPC_UNSUPPORTED("body_set_param(inertia / centre of mass)");
 			return;
 	}
 	_body_changed(body);
+}
+
+// body_reset_mass_properties (bradot_body_3d.cpp:152-160 reset_mass_properties): inertia and centre of mass come from the shape again
+void BradotPhysicsServerCUDA::body_reset_mass_properties(RID p_body) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	body->has_custom_inertia = body->has_custom_com = false;
+	body->mass_override_dirty = true;
+	_body_changed(body);
+}
+
+// the body's own inertia / centre of mass go to its slot before it is described
+void BradotPhysicsServerCUDA::_push_mass_override(Body *p_body) {
+	if (!p_body->mass_override_dirty || p_body->slot < 0) {
+		return;
+	}
+	p_body->mass_override_dirty = false;
+	int32_t slot = p_body->slot;
+	float in[3] = { (float)p_body->custom_inertia.x, (float)p_body->custom_inertia.y, (float)p_body->custom_inertia.z };
+	float cm[3] = { (float)p_body->custom_com.x, (float)p_body->custom_com.y, (float)p_body->custom_com.z };
+	bpc_bodies_set_mass_override(ctx, &slot, 1, nullptr, nullptr);
+	if (p_body->has_custom_inertia || p_body->has_custom_com) {
+		ERR_FAIL_COND_MSG(bpc_bodies_set_mass_override(ctx, &slot, 1, p_body->has_custom_inertia ? in : nullptr, p_body->has_custom_com ? cm : nullptr) < 0, bpc_last_error(ctx));
+	}
 }
 
 Variant BradotPhysicsServerCUDA::body_get_param(RID p_body, BodyParameter p_param) const {
@@ -851,6 +884,17 @@ Variant BradotPhysicsServerCUDA::body_get_param(RID p_body, BodyParameter p_para
 		case BODY_PARAM_ANGULAR_DAMP: return body->ang_damp;
 		case BODY_PARAM_LINEAR_DAMP_MODE: return body->lin_damp_replace ? BODY_DAMP_MODE_REPLACE : BODY_DAMP_MODE_COMBINE;
 		case BODY_PARAM_ANGULAR_DAMP_MODE: return body->ang_damp_replace ? BODY_DAMP_MODE_REPLACE : BODY_DAMP_MODE_COMBINE;
+		case BODY_PARAM_INERTIA:
+		case BODY_PARAM_CENTER_OF_MASS: { // as the body stands on the GPU side (bradot_body_3d.cpp:266-275: _inv_inertia.inverse(), center_of_mass_local)
+			float mp[16];
+			if (body->slot < 0 || bpc_bodies_read(ctx, BPC_FIELD_MASS_PROPS, body->slot, 1, mp) < 0) {
+				return p_param == BODY_PARAM_INERTIA ? (body->has_custom_inertia ? body->custom_inertia : Vector3()) : (body->has_custom_com ? body->custom_com : Vector3());
+			}
+			if (p_param == BODY_PARAM_CENTER_OF_MASS) {
+				return Vector3(mp[4], mp[5], mp[6]);
+			}
+			return body->mode == BODY_MODE_RIGID ? Vector3(1.0f / mp[1], 1.0f / mp[2], 1.0f / mp[3]) : Vector3();
+		}
 		default: return Variant();
 	}
 }
@@ -2517,6 +2561,10 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 					int32_t slot = b->slot, cap = b->max_contacts_reported;
 					bpc_bodies_set_max_contacts_reported(ctx, &slot, 1, &cap);
 				}
+				if (b->has_custom_inertia || b->has_custom_com) {
+					b->mass_override_dirty = true;
+					_body_changed(b); // described once more below, now that the slot its own mass data go with is known
+				}
 			}
 			// exceptions named before both bodies were in a space
 			for (Body *b : uploaded) {
@@ -2538,6 +2586,7 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 			if (b->slot < 0 || !shape_owner.get_or_null(b->shape)) {
 				continue;
 			}
+			_push_mass_override(b);
 			bpc_body_desc d;
 			_fill_desc(b, d);
 			descs.push_back(d);

@@ -133,6 +133,10 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		bool can_sleep = true;
 		bool ccd = false;
 		bool ray_pickable = true;
+		// body_set_param(BODY_PARAM_INERTIA / BODY_PARAM_CENTER_OF_MASS): handed over with bpc_bodies_set_mass_override before the
+		// body is described (anew)
+		Vector3 custom_inertia, custom_com;
+		bool has_custom_inertia = false, has_custom_com = false, mass_override_dirty = false;
 		bool omit_force_integration = false;
 		bool lin_damp_replace = false, ang_damp_replace = false;
 		uint32_t locked_axis = 0;
@@ -351,7 +355,8 @@ public:
 	virtual int body_get_shape_count(RID p_body) const override;
 	virtual void body_attach_object_instance_id(RID p_body, ObjectID p_id) override;
 	virtual ObjectID body_get_object_instance_id(RID p_body) const override;
-	virtual void body_reset_mass_properties(RID p_body) override {}
+	virtual void body_reset_mass_properties(RID p_body) override;
+	void _push_mass_override(Body *p_body);
 	virtual void body_set_collision_layer(RID p_body, uint32_t p_layer) override;
 	virtual uint32_t body_get_collision_layer(RID p_body) const override;
 	virtual void body_set_collision_mask(RID p_body, uint32_t p_mask) override;

@@ -185,6 +185,16 @@ enum { BPC_STATE_TRANSFORM = 0, BPC_STATE_LINEAR_VELOCITY = 1, BPC_STATE_ANGULAR
 int bpc_bodies_set_state(bpc_context *ctx, int state, const int32_t *slots, int n, const float *values);
 /* Gather / scatter variants of the bulk I/O for a list of bodies (state sync of the active bodies only, forces of the pushed
  * bodies only): one staging copy and one kernel whatever n is. */
+/* body_set_param(BODY_PARAM_INERTIA / BODY_PARAM_CENTER_OF_MASS) and body_reset_mass_properties (P3D/bradot_body_3d.cpp:209-229,
+ * update_mass_properties :56-150): a body's own principal inertia and / or local centre of mass in place of the values
+ * computed from its shape.  inertia: n x 3 or NULL (left as it is); all three components > 0 = the body's inertia about
+ * its own axes, otherwise the positive ones replace the diagonal of the computed tensor before it is diagonalised, as in
+ * the reference.  center_of_mass: n x 3 or NULL (left as it is).  Both NULL = body_reset_mass_properties: the centre of mass
+ * is computed again, and so is the inertia -- except that, as in the reference, the positive components given before go
+ * on replacing the diagonal of the computed tensor.  (The reference recomputes the inertia about a new centre of mass only
+ * at its next mass update -- set mass, shape change --; here it is recomputed when the body is described.)  The override
+ * is kept with the slot and takes effect when the body is described next (bpc_bodies_create_slots / bpc_bodies_update). */
+int bpc_bodies_set_mass_override(bpc_context *ctx, const int32_t *slots, int n, const float *inertia, const float *center_of_mass);
 /* The same read, pipelined: _begin queues the read of rows [first, first + n) as they stand after the steps issued so far and
  * returns; the copy to `out` (pinned host memory, or it will not overlap) runs beside whatever is issued next -- the next
  * bpc_step included; _end waits until `out` holds the rows.  One read at a time.  TRANSFORM and the two velocities only.

@@ -1295,6 +1295,18 @@ int main(int argc, char **argv) {
 				case 5:
 					ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, e.v[0] != 0.f);
 					break;
+				case 8:
+					ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_INERTIA, Vector3(e.v[0], e.v[1], e.v[2]));
+					break;
+				case 9:
+					ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_CENTER_OF_MASS, Vector3(e.v[0], e.v[1], e.v[2]));
+					break;
+				case 10:
+					ps->body_reset_mass_properties(body);
+					break;
+				case 11:
+					ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_MASS, e.v[0]);
+					break;
 			}
 		}
 		drive_kinematic(d, w, s, hd.dt, true);

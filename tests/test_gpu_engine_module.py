@@ -148,6 +148,43 @@ def test_engine_module_static_body_with_several_shapes(tmp_path):
     assert np.mean(direct[dyn, 1] > -1.0) > 0.6            # most of them came to lie on the level, not on the plane below
 
 
+def test_engine_module_custom_inertia_and_centre_of_mass(tmp_path):
+    """body_set_param(BODY_PARAM_INERTIA / BODY_PARAM_CENTER_OF_MASS / BODY_PARAM_MASS) and body_reset_mass_properties on bodies
+    that are in a space, through the RID API (the module hands the values over with bpc_bodies_set_mass_override and describes
+    the body anew): the script of test_gpu_features.py::test_custom_inertia_and_centre_of_mass_follow_the_reference, free-running
+    against the reference, positions to 2 mm."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    if not parity.have_oracle():
+        pytest.skip("oracle/_ref/oracle_step not built")
+    sc = scenes.locks_and_damping(24, on_plane=True)
+    sc.bodies["flags"] &= ~np.uint32(63 << scenes.BODY_LOCK_SHIFT)
+    dyn = np.nonzero(sc.bodies["mode"] == scenes.MODE_RIGID)[0]
+    events = []
+    for k, b in enumerate(dyn):
+        rows = {0: [(8, (0.02 + 0.01 * (k % 3), 0.05, 0.03))], 1: [(8, (0.06, 0.0, 0.0)), (9, (0.05, -0.1, 0.0))], 2: [(9, (0.0, -0.15, 0.05))], 3: []}[k % 4]
+        if k % 4 != 3:
+            rows.append((11, (float(sc.bodies["mass"][b]),)))
+        for kind, v in rows:
+            row = np.zeros(12, np.float32)
+            row[:len(v)] = v
+            events.append((2, int(b), kind, row))
+        if k % 4 in (0, 1) and k % 8 < 4:
+            events.append((45, int(b), 10, np.zeros(12, np.float32)))
+    steps = 90
+    path, evp = str(tmp_path / "scene.bscn"), str(tmp_path / "events.bin")
+    sc.write(path)
+    parity.write_events(evp, events)
+    r = subprocess.run([DEMO, path, str(steps), "--events", evp], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    engine = np.array(json.loads(r.stdout.strip().splitlines()[-1])["origins"], np.float32)
+    _, dump = parity.run_oracle(sc, steps, events=events, dump_steps=[steps])
+    _, plain = parity.run_oracle(sc, steps, dump_steps=[steps])
+    ref = dump[("bodies", steps)][:, 9:12]
+    assert np.max(np.abs(engine - ref)) < 2e-3, float(np.abs(engine - ref).max())
+    assert np.max(np.abs(ref - plain[("bodies", steps)][:, 9:12])) > 0.02
+
+
 def test_engine_module_simple_hinges_match_the_reference(tmp_path):
     """joint_make_hinge_simple through the module (the frames built from pivots, axes and body A's transform, as
     joints/bradot_hinge_joint_3d.cpp:69-108 does) against the reference making the same hinges: free-running, positions to 2 mm."""

@@ -156,6 +156,66 @@ def _apply_events(ps, events, step, freed):
             ps.body_set_state([body], server.BODY_STATE_CAN_SLEEP, v[:1])
 
 
+def test_custom_inertia_and_centre_of_mass_follow_the_reference():
+    """body_set_param(BODY_PARAM_INERTIA / BODY_PARAM_CENTER_OF_MASS) and body_reset_mass_properties (bradot_body_3d.cpp:168-172,
+    209-229, update_mass_properties :56-150): tumbling bodies dropped on a plane get, at step 2, a full custom inertia, a
+    partial one with a custom centre of mass, or a centre of mass alone (each followed by a mass write, which is when the
+    reference recomputes the tensor about the new centre); at step 45 some are reset.  Free-running, every step: active flags
+    equal, positions to 2 mm; and the same scene without the script ends up elsewhere."""
+    _need_oracle()
+    sc = scenes.locks_and_damping(24, on_plane=True)
+    sc.bodies["flags"] &= ~np.uint32(63 << scenes.BODY_LOCK_SHIFT)        # no axis locks here: the bodies must be free to turn
+    dyn = np.nonzero(sc.bodies["mode"] == scenes.MODE_RIGID)[0]
+    events = []
+
+    def ev(step, body, kind, v=()):
+        row = np.zeros(12, np.float32)
+        row[:len(v)] = v
+        events.append((step, int(body), kind, row))
+    for k, b in enumerate(dyn):
+        if k % 4 == 0:
+            ev(2, b, 8, (0.02 + 0.01 * (k % 3), 0.05, 0.03))
+        elif k % 4 == 1:
+            ev(2, b, 8, (0.06, 0.0, 0.0))
+            ev(2, b, 9, (0.05, -0.1, 0.0))
+        elif k % 4 == 2:
+            ev(2, b, 9, (0.0, -0.15, 0.05))
+        if k % 4 != 3:
+            ev(2, b, 11, (float(sc.bodies["mass"][b]),))
+        if k % 4 in (0, 1) and k % 8 < 4:
+            ev(45, b, 10)
+    steps = 90
+    _, dump = parity.run_oracle(sc, steps, events=events)
+    _, plain = parity.run_oracle(sc, steps, dump_steps=[steps])
+    assert np.max(np.abs(dump[("bodies", steps)][:, 0:12] - plain[("bodies", steps)][:, 0:12])) > 0.05
+    ps = parity.new_server(sc, dump)
+    for s in range(1, steps + 1):
+        touched = []
+        for (st_, body, kind, v) in events:
+            if st_ != s:
+                continue
+            if kind == 8:
+                ps.bodies_set_mass_override([body], inertia=v[:3])
+            elif kind == 9:
+                ps.bodies_set_mass_override([body], center_of_mass=v[:3])
+            elif kind == 10:
+                ps.bodies_set_mass_override([body])
+            touched.append(body)
+        if touched:
+            touched = sorted(set(touched))
+            ps.bodies_update(touched, sc.bodies[touched])
+        ps.step(sc.dt)
+        ref = dump[("bodies", s)]
+        st = ps.bodies_read_state()
+        assert np.array_equal(st[:, 18], ref[:, 18]), "active flags differ at step %d" % s
+        assert np.max(np.abs(st[:, 9:12] - ref[:, 9:12])) < 2e-3, "positions differ at step %d: %g" % (s, np.max(np.abs(st[:, 9:12] - ref[:, 9:12])))
+    mp = ps.bodies_read(server.FIELD_MASS_PROPS)
+    b0, b2 = int(dyn[4]), int(dyn[2])        # k = 4: full custom inertia, never reset; k = 2: centre of mass alone
+    assert np.allclose(1.0 / mp[b0, 1:4], (0.03, 0.05, 0.03), rtol=1e-6) and np.allclose(mp[b0, 7:16], np.eye(3).reshape(-1))
+    assert np.allclose(mp[b2, 4:7], (0.0, -0.15, 0.05))
+    ps.finish()
+
+
 def test_body_set_state_and_free_follow_the_reference():
     """BradotBody3D::set_state (bradot_body_3d.cpp:352-417) and free(RID) (bradot_physics_server_3d.cpp:1572-1590) at run
     time: a teleported sleeping body wakes, is orthonormalised and gets a new broadphase box; a moved static body wakes what
