@@ -141,6 +141,7 @@ struct AreaRec {
     uint32_t gravity_mode, lin_damp_mode;
     uint32_t ang_damp_mode;
     float gravity, point_unit_distance, lin_damp;
+    uint32_t group, pad_[3]; // non-zero: the areas of a space that share it are the shapes of ONE area (counted once by a body)
     float4 gravity_vector;   // w = angular damp
 };
 

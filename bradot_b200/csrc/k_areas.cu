@@ -211,6 +211,7 @@ static int area_from_desc(bpc_context *ctx, const bpc_area_desc &d, AreaRec &r) 
     r.gravity = d.gravity;
     r.point_unit_distance = d.point_unit_distance;
     r.lin_damp = d.linear_damp;
+    r.group = d.group;
     r.gravity_vector = make_float4(d.gravity_vector[0], d.gravity_vector[1], d.gravity_vector[2], d.angular_damp);
     return 0;
 }

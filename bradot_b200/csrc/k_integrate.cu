@@ -44,7 +44,11 @@ __device__ inline void area_overrides(const AreaRec *__restrict__ areas, const u
     int ac = 0;
     for (uint32_t q = 0; q < cnt && q < AREA_SLOTS; q++) {
         uint32_t e = list[q];
-        if (e & AREA_ATTACHED) idx[ac++] = e & ~AREA_ATTACHED;
+        if (!(e & AREA_ATTACHED)) continue;
+        const uint32_t ai = e & ~AREA_ATTACHED, group = areas[ai].group;
+        bool again = false; // a further shape of an area the body already stands in
+        for (int k = 0; k < ac && group; k++) again = again || areas[idx[k]].group == group;
+        if (!again) idx[ac++] = ai;
     }
     // areas.sort() by priority (AreaCMP, bradot_area_3d.h:223-236); equal priorities: by index here
     for (int i = 1; i < ac; i++) {

@@ -37,7 +37,7 @@ JOINT_EXT_DT = np.dtype([("joint", "<u4"), ("first", "<u4"), ("count", "<u4"), (
 AREA_DT = np.dtype([("space", "<i4"), ("shape", "<i4"), ("flags", "<u4"), ("priority", "<i4"), ("xf", "<f4", 12), ("shape_xf", "<f4", 12),
                     ("layer", "<u4"), ("mask", "<u4"), ("gravity_mode", "<i4"), ("linear_damp_mode", "<i4"), ("angular_damp_mode", "<i4"),
                     ("gravity", "<f4"), ("gravity_vector", "<f4", 3), ("point_unit_distance", "<f4"), ("linear_damp", "<f4"),
-                    ("angular_damp", "<f4"), ("reserved", "<u4")])
+                    ("angular_damp", "<f4"), ("group", "<u4")])   # group: see bpc_area_desc
 AREA_MONITORABLE, AREA_MONITOR_CB, AREA_GRAVITY_POINT, AREA_AREA_MONITOR_CB, AREA_PICKABLE = 1, 2, 4, 8, 16
 JOINT_NO_COLLIDE, JOINT_USE_LIMIT, JOINT_ENABLE_MOTOR, JOINT_HAS_PARAMS = 1, 2, 4, 8
 PIN_DEFAULTS = np.array([0.3, 1.0, 0.0, 0, 0, 0, 0, 0], np.float32)
@@ -962,6 +962,40 @@ def area_zones():
     sc.add_areas(1, shape=zone, xf=at(50.0, -6.0, 0.0), flags=both, layer=8, mask=8)
     sc.add_areas(1, shape=tube, xf=at(50.8, 3.0, 0.3, 0.4), flags=both)
     sc.bodies["mask"] = 0          # no body collides with any other: free flight only (an area looks at the body's LAYER)
+    return sc
+
+
+def area_groups():
+    """Areas of several shapes: in the scene file (and to the C ABI) every further shape is an area record of its own carrying the
+    same non-zero `group` as the record before it; the harness adds it to the area before (area_add_shape).  Bodies in free
+    flight (no masks, nothing touches): a column falls through an area of two overlapping boxes that adds a sideways gravity
+    (a body in both boxes must feel it once), another through an area of two separate spheres that adds linear damping,
+    with a plain replace-gravity zone of higher priority cutting through the first."""
+    sc = Scene(name="area_groups")
+    ball = sc.add_shape(SHAPE_SPHERE, (0.2,))
+    box = sc.add_shape(SHAPE_BOX, (0.2, 0.15, 0.25))
+    slab = sc.add_shape(SHAPE_BOX, (1.5, 0.6, 1.5))
+    orb = sc.add_shape(SHAPE_SPHERE, (0.9,))
+    zone = sc.add_shape(SHAPE_BOX, (0.5, 0.3, 2.0))
+
+    def at(x, y, z):
+        f = IDENT12.copy()
+        f[9], f[10], f[11] = x, y, z
+        return f
+    for k in range(6):
+        sc.add_bodies(1, shape=(ball if k % 2 else box), xf=at(-1.0 + 0.4 * k, 5.0 + 0.5 * k, 0.2 * k), angvel=(0.3, 0.1 * k, 0.0), flags=0, mask=0)
+    for k in range(4):
+        sc.add_bodies(1, shape=ball, xf=at(8.0 + (2.2 if k % 2 else 0.0), 5.0 + 0.7 * k, 0.0), flags=0, mask=0)
+    # area 0 + 1: one area of two overlapping boxes (group 1)
+    common = dict(gravity_mode=1, gravity=3.0, gravity_vector=(1, 0, 0), flags=AREA_MONITOR_CB, priority=0, group=1)
+    sc.add_areas(1, shape=slab, xf=at(0.0, 2.5, 0.0), shape_xf=at(0.0, 0.4, 0.0), **common)
+    sc.add_areas(1, shape=slab, xf=at(0.0, 2.5, 0.0), shape_xf=at(0.3, -0.4, 0.0), **common)
+    # area 2: a plain zone of higher priority through the middle of it: replaces gravity, the walk ends there for gravity
+    sc.add_areas(1, shape=zone, xf=at(0.0, 2.5, 0.0), gravity_mode=3, gravity=2.0, gravity_vector=(0, -1, 0), priority=3, flags=AREA_MONITOR_CB)
+    # area 3 + 4: one area of two separate spheres (group 2): combine linear damping
+    common = dict(linear_damp_mode=1, linear_damp=1.5, flags=AREA_MONITOR_CB | AREA_MONITORABLE, priority=1, group=2)
+    sc.add_areas(1, shape=orb, xf=at(9.0, 2.5, 0.0), shape_xf=at(-1.0, 0.0, 0.0), **common)
+    sc.add_areas(1, shape=orb, xf=at(9.0, 2.5, 0.0), shape_xf=at(1.2, 0.3, 0.0), **common)
     return sc
 
 

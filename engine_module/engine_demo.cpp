@@ -41,7 +41,7 @@ struct ScnBody { uint32_t space, mode, shape, flags; float xf[12], shape_xf[12],
 struct ScnJoint { uint32_t type, body_a, body_b, flags; float fa[12], fb[12], params[8]; uint32_t priority, pad[3]; };
 struct Event { int32_t step, body, kind; float v[12]; }; // kinds 6 / 7 address an area: area_set_transform / free
 struct ScnArea { int32_t space, shape; uint32_t flags; int32_t priority; float xf[12], shape_xf[12]; uint32_t layer, mask; int32_t gravity_mode, linear_damp_mode, angular_damp_mode;
-	float gravity, gravity_vector[3], point_unit_distance, linear_damp, angular_damp; uint32_t reserved; };
+	float gravity, gravity_vector[3], point_unit_distance, linear_damp, angular_damp; uint32_t group; };
 #pragma pack(pop)
 
 // what the areas' monitor callbacks were told: (step whose results were flushed, area, body, status)

@@ -251,7 +251,8 @@ typedef struct bpc_area_desc {
     uint32_t layer, mask;
     int32_t gravity_mode, linear_damp_mode, angular_damp_mode;
     float gravity, gravity_vector[3], point_unit_distance, linear_damp, angular_damp;
-    uint32_t reserved;
+    uint32_t group; /* 0, or: the areas of a space with the same group are the shapes of ONE area -- a body standing in several of
+                     * them has that area once in its override walk (BradotBody3D::add_area counts references, P3D/bradot_body_3d.h) */
 } bpc_area_desc;
 typedef struct bpc_area_event {
     int32_t area, body, status; /* status 0 / 1: body `body` entered / left the area; 2 / 3: AREA `body` entered / left it */

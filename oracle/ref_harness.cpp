@@ -120,7 +120,7 @@ struct ScnArea { // = bpc_area_desc
 	uint32_t layer, mask;
 	int32_t gravity_mode, linear_damp_mode, angular_damp_mode;
 	float gravity, gravity_vector[3], point_unit_distance, linear_damp, angular_damp;
-	uint32_t reserved;
+	uint32_t group; // non-zero and equal to the record before: a further shape of that area, not an area of its own
 };
 #pragma pack(pop)
 
@@ -1163,8 +1163,16 @@ int main(int argc, char **argv) {
 	}
 	for (uint32_t i = 0; i < hd.n_areas; i++) {
 		const ScnArea &a = sareas[i];
+		if (i > 0 && a.group != 0 && sareas[i - 1].group == a.group) { // a further shape of the area before it (added when that one was made)
+			w.areas.push_back(w.areas[i - 1]);
+			w.area_freed.push_back(0);
+			continue;
+		}
 		RID ar = ps->area_create();
 		ps->area_add_shape(ar, w.shapes[a.shape], xf_from(a.shape_xf));
+		for (uint32_t j = i + 1; a.group != 0 && j < hd.n_areas && sareas[j].group == a.group; j++) {
+			ps->area_add_shape(ar, w.shapes[sareas[j].shape], xf_from(sareas[j].shape_xf));
+		}
 		ps->area_set_transform(ar, xf_from(a.xf));
 		ps->area_set_collision_layer(ar, a.layer);
 		ps->area_set_collision_mask(ar, a.mask);

@@ -450,6 +450,45 @@ def test_areas_overrides_and_monitoring_follow_the_reference():
     ps.finish()
 
 
+def test_areas_of_several_shapes_follow_the_reference():
+    """An area with several shapes (area_add_shape beyond the first): to the C ABI every shape is an area record, the records of
+    one area share a `group`, and a body standing in several shapes of the area has it ONCE in its override walk
+    (BradotBody3D::add_area counts references).  scenes.area_groups() free-running beside the reference, where the groups are
+    single areas of two shapes: positions and velocities to 1e-4 after every step, and the monitor callbacks hear the same
+    (area, body, entered / left) events -- per shape there, per record here."""
+    _need_oracle()
+    sc = scenes.area_groups()
+    steps = 110
+    _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1)
+    parent = np.arange(len(sc.areas))
+    for i in range(1, len(sc.areas)):
+        if sc.areas["group"][i] != 0 and sc.areas["group"][i] == sc.areas["group"][i - 1]:
+            parent[i] = parent[i - 1]
+    ps = parity.new_server(sc)
+    heard = 0
+    for k in range(1, steps + 1):
+        ps.step(sc.dt)
+        mine = sorted((int(parent[e[0]]), int(e[1]), int(e[2])) for e in ps.area_events())
+        ref = sorted(tuple(int(x) for x in e) for e in dump.get(("area_events", k), np.zeros((0, 3), np.int32)))
+        assert mine == ref, (k, mine, ref)
+        heard += len(mine)
+        st = ps.bodies_read_state()
+        refb = dump[("bodies", k)]
+        assert np.max(np.abs(st[:, 0:18] - refb[:, 0:18])) < 1e-4, (k, int(np.argmax(np.abs(st[:, 0:18] - refb[:, 0:18]).max(axis=1))))
+    assert heard >= 30
+    st = ps.bodies_read_state()
+    assert np.all(st[0:6, 9] - sc.bodies["xf"][0:6, 9] > 0.05)        # the sideways gravity did act on the first column
+    # with the group ignored (two areas instead of one) a body in both boxes is pushed twice: another trajectory
+    apart = scenes.area_groups()
+    apart.areas["group"] = 0
+    ps2 = parity.new_server(apart)
+    for k in range(steps):
+        ps2.step(sc.dt)
+    assert np.max(np.abs(ps2.bodies_read_state()[0:6, 9] - st[0:6, 9])) > 0.02
+    ps.finish()
+    ps2.finish()
+
+
 def test_static_triangle_meshes_match_the_reference():
     """Static concave colliders (bradot_shape_3d.cpp:1174-1256,1433-1495, bradot_collision_solver_3d.cpp:297-360,
     the four *_face routines of bradot_collision_solver_3d_sat.cpp): spheres, boxes, capsules and hulls on a bumpy 288-triangle
