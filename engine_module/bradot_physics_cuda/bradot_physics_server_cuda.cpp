@@ -2026,17 +2026,19 @@ RID BradotPhysicsServerCUDA::area_create() {
 	return rid;
 }
 
-void BradotPhysicsServerCUDA::_fill_area_desc(const Area *p_area, bpc_area_desc &r_desc) {
+void BradotPhysicsServerCUDA::_fill_area_desc(const Area *p_part, bpc_area_desc &r_desc) {
 	memset(&r_desc, 0, sizeof(r_desc));
+	const Area *p_area = p_part->parent ? p_part->parent : p_part; // a further shape: the area's own values, this record's shape
 	const Space *space = space_owner.get_or_null(p_area->space);
-	Shape *shape = shape_owner.get_or_null(p_area->shape);
+	Shape *shape = shape_owner.get_or_null(p_part->shape);
+	r_desc.group = p_area->group;
 	r_desc.space = space ? space->handle : -1;
 	r_desc.shape = shape ? _shape_handle(shape) : -1;
 	r_desc.flags = (p_area->ray_pickable ? 16u : 0u) | (p_area->monitorable ? 1u : 0u) | (p_area->monitor_callback.is_valid() ? 2u : 0u) | (p_area->gravity_is_point ? 4u : 0u) |
 			(p_area->area_monitor_callback.is_valid() ? 8u : 0u);
 	r_desc.priority = p_area->priority;
 	_xf_to_floats(p_area->xf, r_desc.xf);
-	_xf_to_floats(p_area->shape_xf, r_desc.shape_xf);
+	_xf_to_floats(p_part->shape_xf, r_desc.shape_xf);
 	r_desc.layer = p_area->layer;
 	r_desc.mask = p_area->mask;
 	r_desc.gravity_mode = p_area->gravity_mode;
@@ -2052,8 +2054,18 @@ void BradotPhysicsServerCUDA::_fill_area_desc(const Area *p_area, bpc_area_desc 
 }
 
 // a setter touched the area: upload it if it can be now, else write it again before the next step
+BradotPhysicsServerCUDA::Area *BradotPhysicsServerCUDA::_area_shape_record(Area *p_area, int p_shape_idx) const {
+	if (p_shape_idx == 0) {
+		return p_area->shape.is_valid() ? p_area : nullptr;
+	}
+	return (p_shape_idx > 0 && (uint32_t)p_shape_idx <= p_area->parts.size()) ? p_area->parts[p_shape_idx - 1] : nullptr;
+}
+
 void BradotPhysicsServerCUDA::_area_changed(Area *p_area) {
-	const bool wanted = p_area->space.is_valid() && p_area->shape.is_valid() && !p_area->shape_disabled;
+	for (Area *part : p_area->parts) {
+		_area_changed(part);
+	}
+	const bool wanted = (p_area->parent ? p_area->parent->space : p_area->space).is_valid() && p_area->shape.is_valid() && !p_area->shape_disabled;
 	if (p_area->handle >= 0) {
 		if (!wanted) {
 			_area_leave_space(p_area);
@@ -2068,6 +2080,9 @@ void BradotPhysicsServerCUDA::_area_changed(Area *p_area) {
 }
 
 void BradotPhysicsServerCUDA::_area_leave_space(Area *p_area) {
+	for (Area *part : p_area->parts) {
+		_area_leave_space(part);
+	}
 	if (p_area->pending) {
 		pending_areas.erase(p_area);
 		p_area->pending = false;
@@ -2112,7 +2127,22 @@ void BradotPhysicsServerCUDA::area_add_shape(RID p_area, RID p_shape, const Tran
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
 	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
-	ERR_FAIL_COND_MSG(area->shape.is_valid(), "BradotPhysicsCUDA: an area has one shape (several shapes per object are not built).");
+	if (area->shape.is_valid()) { // a further shape: a record of its own that shares the area's group
+		Area *part = memnew(Area);
+		part->parent = area;
+		part->self = area->self;
+		part->instance_id = area->instance_id;
+		part->shape = p_shape;
+		part->shape_xf = p_transform;
+		part->shape_disabled = p_disabled;
+		part->shape_index = area->parts.size() + 1;
+		if (area->group == 0) {
+			area->group = ++area_group_counter;
+		}
+		area->parts.push_back(part);
+		_area_changed(area); // (the area itself is described anew with its group, the part is uploaded)
+		return;
+	}
 	area->shape = p_shape;
 	area->shape_xf = p_transform;
 	area->shape_disabled = p_disabled;
@@ -2122,51 +2152,75 @@ void BradotPhysicsServerCUDA::area_add_shape(RID p_area, RID p_shape, const Tran
 void BradotPhysicsServerCUDA::area_set_shape(RID p_area, int p_shape_idx, RID p_shape) {
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
-	ERR_FAIL_COND(p_shape_idx != 0 || !area->shape.is_valid());
+	Area *rec = _area_shape_record(area, p_shape_idx);
+	ERR_FAIL_NULL(rec);
 	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
-	area->shape = p_shape;
+	rec->shape = p_shape;
 	_area_changed(area);
 }
 
 void BradotPhysicsServerCUDA::area_set_shape_transform(RID p_area, int p_shape_idx, const Transform3D &p_transform) {
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
-	ERR_FAIL_COND(p_shape_idx != 0 || !area->shape.is_valid());
-	area->shape_xf = p_transform;
+	Area *rec = _area_shape_record(area, p_shape_idx);
+	ERR_FAIL_NULL(rec);
+	rec->shape_xf = p_transform;
 	_area_changed(area);
 }
 
 int BradotPhysicsServerCUDA::area_get_shape_count(RID p_area) const {
 	const Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL_V(area, -1);
-	return area->shape.is_valid() ? 1 : 0;
+	return area->shape.is_valid() ? 1 + (int)area->parts.size() : 0;
 }
 
 RID BradotPhysicsServerCUDA::area_get_shape(RID p_area, int p_shape_idx) const {
 	const Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL_V(area, RID());
-	ERR_FAIL_COND_V(p_shape_idx != 0, RID());
-	return area->shape;
+	const Area *rec = _area_shape_record(const_cast<Area *>(area), p_shape_idx);
+	ERR_FAIL_NULL_V(rec, RID());
+	return rec->shape;
 }
 
 Transform3D BradotPhysicsServerCUDA::area_get_shape_transform(RID p_area, int p_shape_idx) const {
 	const Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL_V(area, Transform3D());
-	ERR_FAIL_COND_V(p_shape_idx != 0, Transform3D());
-	return area->shape_xf;
+	const Area *rec = _area_shape_record(const_cast<Area *>(area), p_shape_idx);
+	ERR_FAIL_NULL_V(rec, Transform3D());
+	return rec->shape_xf;
 }
 
 void BradotPhysicsServerCUDA::area_remove_shape(RID p_area, int p_shape_idx) {
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
-	ERR_FAIL_COND(p_shape_idx != 0 || !area->shape.is_valid());
-	area->shape = RID();
+	ERR_FAIL_NULL(_area_shape_record(area, p_shape_idx));
+	if (area->parts.is_empty()) {
+		area->shape = RID();
+		_area_changed(area);
+		return;
+	}
+	// the shapes behind it move down one index: shift them through the records, drop the last one
+	for (int i = p_shape_idx; i < (int)area->parts.size(); i++) {
+		Area *dst = _area_shape_record(area, i), *src = area->parts[i];
+		dst->shape = src->shape;
+		dst->shape_xf = src->shape_xf;
+		dst->shape_disabled = src->shape_disabled;
+	}
+	Area *last = area->parts[area->parts.size() - 1];
+	_area_leave_space(last);
+	memdelete(last);
+	area->parts.resize(area->parts.size() - 1);
 	_area_changed(area);
 }
 
 void BradotPhysicsServerCUDA::area_clear_shapes(RID p_area) {
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
+	for (Area *part : area->parts) {
+		_area_leave_space(part);
+		memdelete(part);
+	}
+	area->parts.clear();
 	area->shape = RID();
 	_area_changed(area);
 }
@@ -2174,8 +2228,9 @@ void BradotPhysicsServerCUDA::area_clear_shapes(RID p_area) {
 void BradotPhysicsServerCUDA::area_set_shape_disabled(RID p_area, int p_shape_idx, bool p_disabled) {
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
-	ERR_FAIL_COND(p_shape_idx != 0 || !area->shape.is_valid());
-	area->shape_disabled = p_disabled;
+	Area *rec = _area_shape_record(area, p_shape_idx);
+	ERR_FAIL_NULL(rec);
+	rec->shape_disabled = p_disabled;
 	_area_changed(area);
 }
 
@@ -2186,6 +2241,9 @@ void BradotPhysicsServerCUDA::area_attach_object_instance_id(RID p_area, ObjectI
 	Area *area = area_owner.get_or_null(p_area);
 	ERR_FAIL_NULL(area);
 	area->instance_id = p_id;
+	for (Area *part : area->parts) {
+		part->instance_id = p_id;
+	}
 }
 
 ObjectID BradotPhysicsServerCUDA::area_get_object_instance_id(RID p_area) const {
@@ -2377,10 +2435,12 @@ void BradotPhysicsServerCUDA::_flush_area_events() {
 			continue;
 		}
 		uint32_t ai = (uint32_t)(key >> 32);
-		Area *area = ai < area_of_handle.size() ? area_of_handle[ai] : nullptr;
-		if (!area) {
+		Area *record = ai < area_of_handle.size() ? area_of_handle[ai] : nullptr;
+		if (!record) {
 			continue;
 		}
+		Area *area = record->parent ? record->parent : record; // a further shape reports to the area it belongs to, with its index
+		const int area_shape = record->shape_index;
 		if (key & 0x80000000u) { // an area entered / left: the area monitor callback (P3D/bradot_area_3d.cpp:273-310)
 			uint32_t oi = (uint32_t)key & 0x7fffffffu;
 			if (!area->area_monitor_callback.is_valid()) {
@@ -2397,7 +2457,8 @@ void BradotPhysicsServerCUDA::_flush_area_events() {
 			} else {
 				continue;
 			}
-			Variant res[5] = { s > 0 ? AREA_BODY_ADDED : AREA_BODY_REMOVED, other_rid, other_id, 0, 0 };
+			const int other_shape = (oi < area_of_handle.size() && area_of_handle[oi]) ? area_of_handle[oi]->shape_index : 0;
+			Variant res[5] = { s > 0 ? AREA_BODY_ADDED : AREA_BODY_REMOVED, other_rid, other_id, other_shape, area_shape };
 			const Variant *resptr[5] = { &res[0], &res[1], &res[2], &res[3], &res[4] };
 			Callable::CallError ce;
 			Variant ret;
@@ -2420,7 +2481,7 @@ void BradotPhysicsServerCUDA::_flush_area_events() {
 		} else {
 			continue;
 		}
-		Variant res[5] = { s > 0 ? AREA_BODY_ADDED : AREA_BODY_REMOVED, body_rid, body_id, 0, 0 };
+		Variant res[5] = { s > 0 ? AREA_BODY_ADDED : AREA_BODY_REMOVED, body_rid, body_id, b ? b->shape_index : 0, area_shape };
 		const Variant *resptr[5] = { &res[0], &res[1], &res[2], &res[3], &res[4] };
 		Callable::CallError ce;
 		Variant ret;
@@ -2500,6 +2561,10 @@ void BradotPhysicsServerCUDA::free(RID p_rid) {
 	} else if (area_owner.owns(p_rid)) {
 		Area *a = area_owner.get_or_null(p_rid);
 		_area_leave_space(a);
+		for (Area *part : a->parts) {
+			memdelete(part);
+		}
+		a->parts.clear();
 		area_owner.free(p_rid);
 		memdelete(a);
 	} else {

@@ -184,7 +184,8 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		int handle = -1;
 	};
 
-	struct Area { // BradotArea3D (P3D/bradot_area_3d.h:46-70), one shape
+	struct Area { // BradotArea3D (P3D/bradot_area_3d.h:46-70); its further shapes are hidden records (`parts`) that take everything
+		// but shape and shape transform from it and share its `group` on the GPU side (include/bradot_physics_cuda.h: bpc_area_desc.group)
 		RID self, space, shape;
 		Transform3D xf, shape_xf;
 		bool shape_disabled = false;
@@ -196,6 +197,10 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		real_t gravity = 9.80665, point_unit_distance = 0.0, linear_damp = 0.1, angular_damp = 0.1;
 		Vector3 gravity_vector = Vector3(0, -1, 0);
 		Variant wind[4]; // stored, used by soft bodies only
+		Area *parent = nullptr;
+		int shape_index = 0;
+		uint32_t group = 0;
+		LocalVector<Area *> parts;
 		bool pending = false, dirty = false;
 		int handle = -1; // bpc area index once uploaded
 	};
@@ -210,6 +215,8 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	LocalVector<Area *> area_of_handle;
 	HashMap<int32_t, FreedBody> freed_bodies, freed_areas;
 	void _area_changed(Area *p_area);
+	Area *_area_shape_record(Area *p_area, int p_shape_idx) const;
+	uint32_t area_group_counter = 0;
 	void _area_leave_space(Area *p_area);
 	void _fill_area_desc(const Area *p_area, bpc_area_desc &r_desc);
 	void _flush_area_events();

@@ -347,6 +347,11 @@ int main(int argc, char **argv) {
 	g_area_rids = &area_r;
 	for (uint32_t i = 0; i < hd.n_areas; i++) {
 		const ScnArea &a = sareas[i];
+		if (i > 0 && a.group != 0 && sareas[i - 1].group == a.group) { // a further shape of the area before it
+			ps->area_add_shape(area_r.back(), shape_r[a.shape], xf_from(a.shape_xf));
+			area_r.push_back(area_r.back());
+			continue;
+		}
 		RID ar = ps->area_create();
 		ps->area_add_shape(ar, shape_r[a.shape], xf_from(a.shape_xf));
 		ps->area_set_transform(ar, xf_from(a.xf));

@@ -185,6 +185,37 @@ def test_engine_module_custom_inertia_and_centre_of_mass(tmp_path):
     assert np.max(np.abs(ref - plain[("bodies", steps)][:, 9:12])) > 0.02
 
 
+def test_engine_module_areas_of_several_shapes(tmp_path):
+    """area_add_shape beyond the first through the RID API: the module keeps each further shape as an area record of its own that
+    shares the area's group (one override per body, events per shape through the area's own callback).  scenes.area_groups()
+    against the C ABI stepping the same records: the callbacks heard the same (step, area, body, status) events, bodies bit-equal."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    sc = scenes.area_groups()
+    steps = 110
+    path = str(tmp_path / "scene.bscn")
+    sc.write(path)
+    r = subprocess.run([DEMO, path, str(steps)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    heard = sorted(tuple(e) for e in out["area_events"])
+    parent = np.arange(len(sc.areas))
+    for i in range(1, len(sc.areas)):
+        if sc.areas["group"][i] != 0 and sc.areas["group"][i] == sc.areas["group"][i - 1]:
+            parent[i] = parent[i - 1]
+    ps = parity.new_server(sc)
+    mine = []
+    for s in range(1, steps + 1):
+        ps.step(sc.dt)
+        mine += [(s, int(parent[e[0]]), int(e[1]), int(e[2])) for e in ps.area_events()]
+    st = ps.bodies_read_state()
+    ps.finish()
+    assert heard == sorted(mine), (sorted(set(heard) - set(mine)), sorted(set(mine) - set(heard)))
+    assert len(heard) >= 30
+    engine = np.array(out["origins"], np.float32)
+    assert np.array_equal(engine, st[:, 9:12]), float(np.abs(engine - st[:, 9:12]).max())
+
+
 def test_engine_module_simple_hinges_match_the_reference(tmp_path):
     """joint_make_hinge_simple through the module (the frames built from pivots, axes and body A's transform, as
     joints/bradot_hinge_joint_3d.cpp:69-108 does) against the reference making the same hinges: free-running, positions to 2 mm."""
