@@ -384,6 +384,7 @@ int bpc_flush_area_tables(bpc_context *ctx) {
                 for (uint32_t q = p + 1; q < start[s + 1]; q++) {
                     const AreaRec &ra = ctx->h_areas[list[p]], &rb = ctx->h_areas[list[q]];
                     if (!(ra.flags & rb.flags & AF_ALIVE) || !((ra.flags | rb.flags) & AF_MOVED) || !((ra.flags | rb.flags) & AF_MONITORABLE)) continue;
+                    if (ra.group != 0u && ra.group == rb.group) continue; // two shapes of ONE area: an object never pairs with itself
                     ctx->aa_cand.push_back({ list[p], list[q], ra.flags, rb.flags, ra.layer, ra.mask, rb.layer, rb.mask });
                 }
             }

@@ -969,7 +969,7 @@ def area_groups():
     """Areas of several shapes: in the scene file (and to the C ABI) every further shape is an area record of its own carrying the
     same non-zero `group` as the record before it; the harness adds it to the area before (area_add_shape).  Bodies in free
     flight (no masks, nothing touches): a column falls through an area of two overlapping boxes that adds a sideways gravity
-    (a body in both boxes must feel it once), another through an area of two separate spheres that adds linear damping,
+    (a body in both boxes must feel it once), another through an area of two overlapping spheres that adds linear damping and watches areas (its own shapes must not be told of each other),
     with a plain replace-gravity zone of higher priority cutting through the first."""
     sc = Scene(name="area_groups")
     ball = sc.add_shape(SHAPE_SPHERE, (0.2,))
@@ -993,9 +993,9 @@ def area_groups():
     # area 2: a plain zone of higher priority through the middle of it: replaces gravity, the walk ends there for gravity
     sc.add_areas(1, shape=zone, xf=at(0.0, 2.5, 0.0), gravity_mode=3, gravity=2.0, gravity_vector=(0, -1, 0), priority=3, flags=AREA_MONITOR_CB)
     # area 3 + 4: one area of two separate spheres (group 2): combine linear damping
-    common = dict(linear_damp_mode=1, linear_damp=1.5, flags=AREA_MONITOR_CB | AREA_MONITORABLE, priority=1, group=2)
-    sc.add_areas(1, shape=orb, xf=at(9.0, 2.5, 0.0), shape_xf=at(-1.0, 0.0, 0.0), **common)
-    sc.add_areas(1, shape=orb, xf=at(9.0, 2.5, 0.0), shape_xf=at(1.2, 0.3, 0.0), **common)
+    common = dict(linear_damp_mode=1, linear_damp=1.5, flags=AREA_MONITOR_CB | AREA_MONITORABLE | AREA_AREA_MONITOR_CB, priority=1, group=2)   # (its two shapes overlap nothing but could be told of each other: they must not)
+    sc.add_areas(1, shape=orb, xf=at(9.0, 2.5, 0.0), shape_xf=at(-0.8, 0.0, 0.0), **common)
+    sc.add_areas(1, shape=orb, xf=at(9.0, 2.5, 0.0), shape_xf=at(0.8, 0.3, 0.0), **common)
     return sc
 
 
