@@ -298,7 +298,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 		r.rid = is_area ? server->area_of_handle[area_handle]->self : server->body_of_slot[out[i].body]->self;
 		r.collider_id = is_area ? server->area_of_handle[area_handle]->instance_id : server->body_of_slot[out[i].body]->instance_id;
 		r.collider = r.collider_id.is_valid() ? ObjectDB::get_instance(r.collider_id) : nullptr;
-		r.shape = is_area ? 0 : server->body_of_slot[out[i].body]->shape_index;
+		r.shape = is_area ? server->area_of_handle[area_handle]->shape_index : server->body_of_slot[out[i].body]->shape_index;
 		r.face_index = -1;
 	}
 	return hits;
@@ -326,7 +326,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_
 				r_results[cc].rid = server->area_of_handle[ah]->self;
 				r_results[cc].collider_id = server->area_of_handle[ah]->instance_id;
 				r_results[cc].collider = r_results[cc].collider_id.is_valid() ? ObjectDB::get_instance(r_results[cc].collider_id) : nullptr;
-				r_results[cc].shape = 0;
+				r_results[cc].shape = server->area_of_handle[ah]->shape_index;
 				cc++;
 			}
 			continue;
