@@ -40,6 +40,10 @@ struct QsArgs {
     // rest_info / cast_motion
     const float *motions; // n x 3 (may be null: no motion)
     float margin;
+    // collide_with_areas / collide_with_bodies (intersect_shape only): the areas of the space, tested after the bodies
+    uint32_t flags;
+    const AreaRec *areas;
+    const uint32_t *area_list, *area_start;
     const BodyVel *vel;
     const BodyMassW *massw;
     bpc_rest_info *rest_out;
@@ -86,6 +90,21 @@ __device__ inline void qs_candidate(const QsArgs &a, uint32_t j, const Sh &qs, c
     cc++;
 }
 
+
+// an area as a candidate of intersect_shape (the answer's entry is -2 - area index)
+__device__ inline void qs_area_candidate(const QsArgs &a, uint32_t ai, const Sh &qs, const X3 &qx, uint32_t r, int &cc) {
+    if (cc >= (int)a.max_results) return;
+    const AreaRec &ar = a.areas[ai];
+    if (!(ar.flags & AF_ALIVE) || !(ar.layer & a.mask)) return;
+    X3 xb(M3(f4v(ar.s0), f4v(ar.s1), f4v(ar.s2)), f4v(ar.so));
+    Sh sb = qs_shape(a, ar.shape_type, ar.shape_p);
+    Manifold *none = nullptr;
+    bool hit = a.margin != 0.f ? solve_static<true, true, true>(qs, qx, sb, xb, *none, nullptr, nullptr, nullptr, a.margin, 0.f)
+                               : solve_static<true, false, true>(qs, qx, sb, xb, *none, nullptr);
+    if (!hit) return;
+    a.bodies[(size_t)r * a.max_results + cc] = -2 - (int32_t)ai;
+    cc++;
+}
 
 // Every leaf of the tree (and every unbounded static of the space) whose stored box meets [qmin, qmax]: f(body index).
 template <typename F>
@@ -352,8 +371,10 @@ __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
     const float grow = 1e-4f + a.margin; // the box test only nominates candidates
     V3 qmin = box.pos - V3(grow, grow, grow), qmax = box.pos + box.size + V3(grow, grow, grow);
     int cc = 0;
-    for (uint32_t k = a.big_start[a.space], ke = a.big_start[a.space + 1]; k < ke; k++) qs_candidate(a, a.big[k], qs, qx, r, cc);
-    if (a.n_tree == 1) {
+    const bool bodies = !(a.flags & BPC_QUERY_NO_BODIES);
+    for (uint32_t k = a.big_start[a.space], ke = a.big_start[a.space + 1]; k < ke && bodies; k++) qs_candidate(a, a.big[k], qs, qx, r, cc);
+    if (!bodies) {
+    } else if (a.n_tree == 1) {
         qs_candidate(a, __float_as_uint(a.leaf_min[0].w), qs, qx, r, cc);
     } else if (a.n_tree > 1) {
         uint32_t stack[128]; // as deep as the traversal of the step: key length plus the index tie-break
@@ -383,6 +404,9 @@ __global__ void __launch_bounds__(QS_THREADS) k_intersect_shapes(QsArgs a) {
                 node = stack[--sp];
             }
         }
+    }
+    if (a.flags & BPC_QUERY_AREAS) {
+        for (uint32_t k = a.area_start[a.space], ke = a.area_start[a.space + 1]; k < ke; k++) qs_area_candidate(a, a.area_list[k], qs, qx, r, cc);
     }
     a.counts[r] = cc;
 }
@@ -473,7 +497,7 @@ __global__ void __launch_bounds__(QS_THREADS) k_collide_shapes(QcArgs c) {
 }
 
 extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
-                                          float margin, int max_results, int32_t *out_counts, int32_t *out_bodies) {
+                                          int flags, float margin, int max_results, int32_t *out_counts, int32_t *out_bodies) {
     if (!ctx) return -1;
     if (space < 0 || (size_t)space >= ctx->spaces.size()) {
         ctx->err = "bpc_space_intersect_shapes: no such space";
@@ -494,6 +518,8 @@ extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, co
     cudaStream_t st = ctx->stream;
     if (bpc_flush_tables(ctx)) return -1; // a query shape may have been created after the last body
     if (bpc_build_tree(ctx)) return -1;
+    if (ctx->h_areas.empty()) flags &= ~BPC_QUERY_AREAS;
+    if ((flags & BPC_QUERY_AREAS) && bpc_flush_area_tables(ctx)) return -1;
     size_t id_words = ((size_t)n + 3) & ~(size_t)3, xf_words = (size_t)n * 12, body_words = (size_t)n * max_results;
     ctx->staging.reserve(id_words * 2 + xf_words + body_words + 16, false, st);
     if (!ctx->staging.p) {
@@ -508,6 +534,10 @@ extern "C" int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, co
     a.max_results = (uint32_t)max_results;
     a.margin = margin;
     a.motions = nullptr;
+    a.flags = (uint32_t)flags;
+    a.areas = ctx->d_areas.p;
+    a.area_list = ctx->area_list.p;
+    a.area_start = ctx->area_start.p;
     int32_t *d_ids = (int32_t *)ctx->staging.p;
     float *d_xf = ctx->staging.p + id_words;
     a.shape_ids = d_ids;

@@ -124,7 +124,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_step.argtypes = [vp, cf]
     lib.bpc_space_intersect_rays.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, vp]
     lib.bpc_space_intersect_points.argtypes = [vp, ci, ci, vp, ctypes.c_uint, ci, ci, vp, vp]
-    lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
+    lib.bpc_space_intersect_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, ci, cf, ci, vp, vp]
     lib.bpc_space_collide_shapes.argtypes = [vp, ci, ci, vp, vp, ctypes.c_uint, cf, ci, vp, vp]
     lib.bpc_space_set_query_exclude.argtypes = [vp, vp, ci]
     lib.bpc_bodies_test_motion.argtypes = [vp, ci, vp, vp]
@@ -442,15 +442,17 @@ class PhysicsServerCUDA:
                                                         (8 if areas else 0) | (0 if with_bodies else 16), int(max_results), _ptr(counts), _ptr(bodies)))
         return counts, bodies
 
-    def intersect_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=32, margin=0.0):
-        """Batched PhysicsDirectSpaceState3D.intersect_shape: shape handles (n) placed at xforms (n, 12)."""
+    def intersect_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=32, margin=0.0, areas=False, bodies=True):
+        """Batched PhysicsDirectSpaceState3D.intersect_shape: shape handles (n) placed at xforms (n, 12); with `areas`, areas are
+        listed too, as -2 - area index."""
+        with_bodies = bodies
         sh = np.ascontiguousarray(shapes, np.int32).reshape(-1)
         xf = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
         assert len(sh) == len(xf)
         counts = np.zeros(len(sh), np.int32)
         bodies = np.full((len(sh), max_results), -1, np.int32)
         self._check(self.lib.bpc_space_intersect_shapes(self.ctx, int(space), len(sh), _ptr(sh), _ptr(xf), ctypes.c_uint(collision_mask),
-                                                        ctypes.c_float(margin), int(max_results), _ptr(counts), _ptr(bodies)))
+                                                        (8 if areas else 0) | (0 if with_bodies else 16), ctypes.c_float(margin), int(max_results), _ptr(counts), _ptr(bodies)))
         return counts, bodies
 
     def collide_shapes(self, shapes, xforms, space=0, collision_mask=0xFFFFFFFF, max_results=16, margin=0.0):

@@ -345,8 +345,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_
 
 int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_parameters, ShapeResult *r_results, int p_result_max) {
 	ERR_FAIL_NULL_V(server, 0);
-	ERR_FAIL_COND_V_MSG(p_parameters.collide_with_areas, 0, "BradotPhysicsCUDA: intersect_shape with areas is not supported yet.");
-	if (p_result_max <= 0 || !p_parameters.collide_with_bodies) {
+	if (p_result_max <= 0 || (!p_parameters.collide_with_bodies && !p_parameters.collide_with_areas)) {
 		return 0;
 	}
 	BradotPhysicsServerCUDA::Shape *shape = server->shape_owner.get_or_null(p_parameters.shape_rid);
@@ -362,9 +361,22 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_shape(const ShapeParameters &p_
 	slots.resize(max_r);
 	LocalVector<int32_t> excluded;
 	BpcExcludeScope exclude_scope(server, server->ctx, p_parameters.exclude, excluded);
-	ERR_FAIL_COND_V_MSG(bpc_space_intersect_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, p_parameters.margin, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
+	ERR_FAIL_COND_V_MSG(bpc_space_intersect_shapes(server->ctx, space_handle, 1, &handle, f, p_parameters.collision_mask, (p_parameters.collide_with_areas ? BPC_QUERY_AREAS : 0) | (p_parameters.collide_with_bodies ? 0 : BPC_QUERY_NO_BODIES), p_parameters.margin, max_r, &count, slots.ptr()) < 0, 0, bpc_last_error(server->ctx));
 	int cc = 0;
 	for (int i = 0; i < count; i++) {
+		if (slots[i] <= -2) { // an area
+			const int ah = -2 - slots[i];
+			if ((uint32_t)ah < server->area_of_handle.size() && server->area_of_handle[ah]) {
+				if (r_results) {
+					r_results[cc].rid = server->area_of_handle[ah]->self;
+					r_results[cc].collider_id = server->area_of_handle[ah]->instance_id;
+					r_results[cc].collider = r_results[cc].collider_id.is_valid() ? ObjectDB::get_instance(r_results[cc].collider_id) : nullptr;
+					r_results[cc].shape = server->area_of_handle[ah]->shape_index;
+				}
+				cc++;
+			}
+			continue;
+		}
 		if (slots[i] < 0 || (uint32_t)slots[i] >= server->body_of_slot.size() || !server->body_of_slot[slots[i]]) {
 			continue;
 		}

@@ -356,9 +356,9 @@ int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *
  * modules/bradot_physics_3d/bradot_space_3d.cpp:208-262), batched: query i is shape handle shapes[i] (from bpc_shape_create*)
  * placed at xforms[i] (12 floats, basis rows + origin), grown by `margin` (0 = the plain routines, else the reference's withMargin
  * variants); the answer lists the bodies whose shape it overlaps.
- * Output layout as bpc_space_intersect_points. */
+ * Output layout and flags (BPC_QUERY_AREAS / BPC_QUERY_NO_BODIES) as bpc_space_intersect_points. */
 int bpc_space_intersect_shapes(bpc_context *ctx, int space, int n, const int32_t *shapes, const float *xforms, unsigned collision_mask,
-                               float margin, int max_results, int32_t *out_counts, int32_t *out_bodies);
+                               int flags, float margin, int max_results, int32_t *out_counts, int32_t *out_bodies);
 
 /* PhysicsDirectSpaceState3D::collide_shape (servers/physics_server_3d.h; implementation
  * modules/bradot_physics_3d/bradot_space_3d.cpp:383-431), batched: for each query shape (grown by `margin`) the contact pairs with

@@ -703,6 +703,31 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 		}
 	}
 	d.arr("shape_queries_margin", step, "i4", { (uint64_t)n, 9 }, sqm.data(), sqm.size() * 4);
+	if (!w.areas.empty()) { // "shape_queries_areas": intersect_shape with collide_with_areas, up to 16 results, areas as -2 - index
+		std::map<RID, int> aidx;
+		for (size_t i = 0; i < w.areas.size(); i++) {
+			if (aidx.find(w.areas[i]) == aidx.end()) {
+				aidx[w.areas[i]] = (int)i;
+			}
+		}
+		std::vector<int32_t> sqa(n * 17, -1);
+		for (size_t i = 0; i < n; i++) {
+			PhysicsDirectSpaceState3D::ShapeParameters sp;
+			sp.shape_rid = qshape[i % 3];
+			sp.transform = xf_from(&sxf[i * 12]);
+			sp.collision_mask = 0xffffffffu;
+			sp.collide_with_areas = true;
+			PhysicsDirectSpaceState3D::ShapeResult sr[16];
+			int cc = ds ? ds->intersect_shape(sp, sr, 16) : 0;
+			sqa[i * 17] = cc;
+			for (int k = 0; k < cc; k++) {
+				auto it = rid_index.find(sr[k].rid);
+				auto ita = aidx.find(sr[k].rid);
+				sqa[i * 17 + 1 + k] = it != rid_index.end() ? it->second : (ita != aidx.end() ? -2 - ita->second : -1);
+			}
+		}
+		d.arr("shape_queries_areas", step, "i4", { (uint64_t)n, 17 }, sqa.data(), sqa.size() * 4);
+	}
 	d.arr("rays_excl", step, "i4", { (uint64_t)n, 2 }, ex_r.data(), ex_r.size() * 4);
 	d.arr("shapes_excl", step, "i4", { (uint64_t)n, 9 }, ex_s.data(), ex_s.size() * 4);
 	d.arr("shape_collide", step, "f4", { (uint64_t)n, 1 + 16 * 6 }, cs.data(), cs.size() * 4);

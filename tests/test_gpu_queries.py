@@ -124,6 +124,15 @@ def test_rays_and_points_with_areas():
         differ = sum(set(listed[i, :counts[i]].tolist()) != set(refp[i, 1:1 + refp[i, 0]].tolist()) for i in range(n))
         assert differ <= 3, (k, differ)
         assert (refp[:, 1:] <= -2).sum() > 400
+        # intersect_shape with collide_with_areas: the query shapes of the dump at its transforms
+        xf = dump[("shape_query_xf", k)]
+        if k == 1:
+            shape_of = _shape_queries(ps, rays)
+        cs, ls = ps.intersect_shapes(shape_of, xf, max_results=16, areas=True)
+        refs = dump[("shape_queries_areas", k)]
+        differ = sum(set(ls[i, :cs[i]].tolist()) != set(refs[i, 1:1 + refs[i, 0]].tolist()) for i in range(n))
+        assert differ <= n // 500, (k, differ)
+        assert (refs[:, 1:] <= -2).sum() > 600
     ps.finish()
     assert area_hits > 500
 
