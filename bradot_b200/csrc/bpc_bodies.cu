@@ -531,6 +531,12 @@ extern "C" int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n)
         ctx->free_slots.push_back(i);
         gone[i] = 1;
     }
+    if (!ctx->h_same.empty()) {
+        size_t before = ctx->h_same.size();
+        ctx->h_same.erase(std::remove_if(ctx->h_same.begin(), ctx->h_same.end(), [&](uint64_t k) { return gone[(uint32_t)(k >> 32)] || gone[(uint32_t)k]; }),
+                          ctx->h_same.end());
+        ctx->same_dirty = ctx->same_dirty || before != ctx->h_same.size();
+    }
     // collision exceptions that name a destroyed body go with it (the joints' ones with their joints)
     ctx->h_except_user.erase(std::remove_if(ctx->h_except_user.begin(), ctx->h_except_user.end(),
                                             [&](uint64_t k) { return gone[(uint32_t)(k >> 32)] || gone[(uint32_t)k]; }),
@@ -1110,6 +1116,20 @@ __global__ void k_scatter_forces(uint32_t n, const uint32_t *__restrict__ slots,
 
 // Pipelined read-back: the rows are packed on the main stream into a buffer of their own, the copy to the host runs on a side
 // stream, so the next step's kernels do not wait for the bus (nor the copy for them).
+extern "C" int bpc_bodies_set_same_object(bpc_context *ctx, int body_a, int body_b, int same) {
+    if (!ctx) return -1;
+    if (body_a < 0 || body_b < 0 || (uint32_t)body_a >= ctx->n_bodies || (uint32_t)body_b >= ctx->n_bodies || body_a == body_b || ctx->h_dead[body_a] || ctx->h_dead[body_b])
+        return fail(ctx, "bpc_bodies_set_same_object: invalid body");
+    uint64_t key = ((uint64_t)std::min(body_a, body_b) << 32) | (uint32_t)std::max(body_a, body_b);
+    auto it = std::lower_bound(ctx->h_same.begin(), ctx->h_same.end(), key);
+    bool have = it != ctx->h_same.end() && *it == key;
+    if (same && !have) ctx->h_same.insert(it, key);
+    else if (!same && have) ctx->h_same.erase(it);
+    else return 0;
+    ctx->same_dirty = true;
+    return 0;
+}
+
 extern "C" int bpc_bodies_set_mass_override(bpc_context *ctx, const int32_t *slots, int n, const float *inertia, const float *center_of_mass) {
     if (!ctx) return -1;
     if (n < 0 || (n > 0 && !slots)) return fail(ctx, "bpc_bodies_set_mass_override: bad arguments");

@@ -251,6 +251,9 @@ struct bpc_context {
     std::vector<JointRec> h_joints;
     struct MassOverride { float inertia[3]; float com[3]; bool has_inertia, has_com, partial; }; // partial: after a reset (see bpc_bodies_set_mass_override)
     std::unordered_map<uint32_t, MassOverride> h_mass_override; // body_set_param(INERTIA / CENTER_OF_MASS), by slot
+    std::vector<uint64_t> h_same; // sorted (a << 32 | b), a < b: records that are shapes of one object and never pair
+    DevBuf<uint64_t> d_same;
+    bool same_dirty = false;
     std::vector<float> h_shape_bias; // shape_set_custom_solver_bias per shape; empty until one is set
     DevBuf<float> d_shape_bias;
     std::vector<float> h_jext; // JEXT_STRIDE values per joint, present once a joint with a long parameter table exists

@@ -292,6 +292,22 @@ __global__ void __launch_bounds__(BP_THREADS) k_traverse(int n, const float4 *__
     em.flush();
 }
 
+// the found pairs without those of two records of one object (a sorted key list, searched per pair; order does not matter: the sort follows)
+__global__ void __launch_bounds__(BP_THREADS) k_drop_same(uint32_t n, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ same, uint32_t n_same,
+                                                          uint64_t *__restrict__ out, uint32_t *__restrict__ counter) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t k = keys[i];
+    uint32_t lo = 0, hi = n_same;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (same[mid] < k) lo = mid + 1;
+        else hi = mid;
+    }
+    if (lo < n_same && same[lo] == k) return;
+    out[atomicAdd(counter, 1u)] = k;
+}
+
 // Run of each body (as the pair's A) in the previous, sorted pair list: the lookup of k_match then
 // searches a handful of keys instead of the whole list.
 __global__ void __launch_bounds__(BP_THREADS) k_a_ranges(uint32_t n_old, const uint64_t *__restrict__ kold, uint32_t *__restrict__ a_begin,
@@ -428,6 +444,17 @@ int bpc_launch_broadphase(bpc_context *ctx) {
     if (found > ctx->pair_cap) {
         ctx->err = "broadphase: pair buffer overflow";
         return -1;
+    }
+    // records that are shapes of one object (bpc_bodies_set_same_object) are taken out of the found list here, off the
+    // traversal's path: scenes without such records (all but the engine module's many-shaped kinematic bodies) never come here
+    if (!ctx->h_same.empty() && found) {
+        BPC_CHECK(cudaMemsetAsync(ctx->counters.p + CNT_PAIRS, 0, sizeof(uint32_t), st));
+        k_drop_same<<<nblk(found, BP_THREADS), BP_THREADS, 0, st>>>(found, ctx->pair_keys_raw.p, ctx->d_same.p, (uint32_t)ctx->h_same.size(), ctx->pair_keys[nxt].p,
+                                                                    ctx->counters.p + CNT_PAIRS);
+        ctx->launches += 1;
+        BPC_CHECK(cudaMemcpyAsync(&found, ctx->counters.p + CNT_PAIRS, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        BPC_CHECK(cudaStreamSynchronize(st));
+        if (found) BPC_CHECK(cudaMemcpyAsync(ctx->pair_keys_raw.p, ctx->pair_keys[nxt].p, (size_t)found * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
     }
     // canonical order: sort by (A << 32 | B); only the digits that can be non-zero are visited
     int bits = 1;

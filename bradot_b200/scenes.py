@@ -431,9 +431,12 @@ def sleepers(n_boxes=6):
     return sc
 
 
-def kinematic_platform():
+def kinematic_platform(rails=False):
     """A kinematic platform (moved by body_set_state(TRANSFORM) every step: 0.6 m/s along x, 0.3 rad/s about y, scripted
-    through its scene velocities) carrying boxes and spheres over a ground plane; a second kinematic box stands still."""
+    through its scene velocities) carrying boxes and spheres over a ground plane; a second kinematic box stands still.
+    rails: the platform has two further shapes, rails along two of its edges (records flagged BODY_FURTHER_SHAPE: one kinematic
+    body of three shapes to the harness and the engine demo, three kinematic records moved alike and marked as one object
+    to the C ABI)."""
     sc = Scene(name="kinematic_platform")
     sc.add_static_plane((0, 1, 0), 0.0)
     slab = sc.add_shape(SHAPE_BOX, (2.0, 0.2, 2.0, 0))
@@ -442,6 +445,12 @@ def kinematic_platform():
     x = IDENT12.copy()
     x[10] = 1.0
     sc.add_bodies(1, mode=MODE_KINEMATIC, shape=slab, xf=x, linvel=(0.6, 0.0, 0.0), angvel=(0.0, 0.3, 0.0))
+    if rails:
+        rail = sc.add_shape(SHAPE_BOX, (0.1, 0.3, 2.0, 0))
+        for side in (-1.0, 1.0):
+            sx = IDENT12.copy()
+            sx[9], sx[10] = 1.9 * side, 0.5
+            sc.add_bodies(1, mode=MODE_KINEMATIC, shape=rail, xf=x, shape_xf=sx, linvel=(0.6, 0.0, 0.0), angvel=(0.0, 0.3, 0.0), flags=1 | BODY_FURTHER_SHAPE)
     x2 = IDENT12.copy()
     x2[9], x2[10] = 6.0, 0.5
     sc.add_bodies(1, mode=MODE_KINEMATIC, shape=slab, xf=x2)   # never moved: stays inactive

@@ -671,7 +671,7 @@ void BradotPhysicsServerCUDA::body_set_mode(RID p_body, BodyMode p_mode) {
 	if (body->mode == p_mode) {
 		return;
 	}
-	ERR_FAIL_COND_MSG(!body->parts.is_empty() && p_mode != BODY_MODE_STATIC, "BradotPhysicsCUDA: only static bodies can have several shapes in this version.");
+	ERR_FAIL_COND_MSG(!body->parts.is_empty() && p_mode > BODY_MODE_KINEMATIC, "BradotPhysicsCUDA: only static and kinematic bodies can have several shapes in this version.");
 	body->mode = p_mode;
 	_body_changed(body);
 }
@@ -687,8 +687,8 @@ void BradotPhysicsServerCUDA::body_add_shape(RID p_body, RID p_shape, const Tran
 	ERR_FAIL_NULL(body);
 	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
 	ERR_FAIL_COND_MSG(p_disabled, "BradotPhysicsCUDA: disabled shapes are not supported yet.");
-	if (body->shape.is_valid()) { // a further shape: static bodies only, as a record of its own
-		ERR_FAIL_COND_MSG(body->mode != BODY_MODE_STATIC, "BradotPhysicsCUDA: only static bodies can have several shapes in this version.");
+	if (body->shape.is_valid()) { // a further shape: bodies without dynamics only (static, kinematic), as a record of its own
+		ERR_FAIL_COND_MSG(body->mode > BODY_MODE_KINEMATIC, "BradotPhysicsCUDA: only static and kinematic bodies can have several shapes in this version.");
 		Body *part = memnew(Body);
 		part->parent = body;
 		part->self = body->self;
@@ -952,8 +952,8 @@ void BradotPhysicsServerCUDA::body_set_state(RID p_body, BodyState p_state, cons
 	}
 	int32_t slot = body->slot;
 	ERR_FAIL_COND_MSG(bpc_bodies_set_state(ctx, (int)p_state, &slot, 1, f) < 0, bpc_last_error(ctx));
-	for (Body *part : body->parts) { // the further shapes of a static body are placed with it
-		if (part->slot >= 0 && p_state == BODY_STATE_TRANSFORM) {
+	for (Body *part : body->parts) { // the further shapes of a static or kinematic body are placed, and moved, with it
+		if (part->slot >= 0 && (p_state == BODY_STATE_TRANSFORM || p_state == BODY_STATE_LINEAR_VELOCITY || p_state == BODY_STATE_ANGULAR_VELOCITY)) {
 			int32_t ps = part->slot;
 			ERR_FAIL_COND_MSG(bpc_bodies_set_state(ctx, (int)p_state, &ps, 1, f) < 0, bpc_last_error(ctx));
 		}
@@ -2641,6 +2641,21 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 				if (b->has_custom_inertia || b->has_custom_com) {
 					b->mass_override_dirty = true;
 					_body_changed(b); // described once more below, now that the slot its own mass data go with is known
+				}
+			}
+			// the records of one body never pair with each other (static ones would not anyway: this is for kinematic bodies)
+			for (Body *b : uploaded) {
+				Body *owner = b->parent ? b->parent : b;
+				if (owner->parts.is_empty()) {
+					continue;
+				}
+				if (owner != b && owner->slot >= 0) {
+					bpc_bodies_set_same_object(ctx, b->slot, owner->slot, 1);
+				}
+				for (Body *other : owner->parts) {
+					if (other != b && other->slot >= 0) {
+						bpc_bodies_set_same_object(ctx, b->slot, other->slot, 1);
+					}
 				}
 			}
 			// exceptions named before both bodies were in a space

@@ -103,11 +103,17 @@ static Transform3D xf_from(const float *f) {
 
 int main(int argc, char **argv) {
 	if (argc < 3) {
-		fprintf(stderr, "usage: engine_demo scene.bscn steps [--events events.bin]\n");
+		fprintf(stderr, "usage: engine_demo scene.bscn steps [--events events.bin] [--drive-kinematic]\n");
 		return 2;
 	}
 	int steps = atoi(argv[2]);
 	std::vector<Event> events;
+	// --drive-kinematic: kinematic bodies are moved by body_set_state(TRANSFORM) before every step, their scene velocities being
+	// the script (rotation about y by angvel.y t, origin + linvel t), exactly as oracle/ref_harness.cpp drives them
+	bool drive_kinematic = false;
+	for (int i = 3; i < argc; i++) {
+		drive_kinematic = drive_kinematic || strcmp(argv[i], "--drive-kinematic") == 0;
+	}
 	for (int i = 3; i + 1 < argc; i++) {
 		if (strcmp(argv[i], "--events") == 0) {
 			FILE *ef = fopen(argv[i + 1], "rb");
@@ -223,6 +229,10 @@ int main(int argc, char **argv) {
 		}
 		shape_r.push_back(sh);
 	}
+	std::vector<int> kin_body;
+	std::vector<Transform3D> kin_xf0;
+	std::vector<Vector3> kin_lin;
+	std::vector<float> kin_wy;
 	for (const ScnBody &b : bodies) {
 		if ((b.flags & 0x4000) && !body_r.empty()) { // bit14: a further shape of the (static) body before it
 			ps->body_add_shape(body_r.back(), shape_r[b.shape], xf_from(b.shape_xf), false);
@@ -241,8 +251,15 @@ int main(int argc, char **argv) {
 		ps->body_set_collision_layer(body, b.layer);
 		ps->body_set_collision_mask(body, b.mask);
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_TRANSFORM, xf_from(b.xf));
-		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
-		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(b.angvel[0], b.angvel[1], b.angvel[2]));
+		if (drive_kinematic && b.mode == (uint32_t)PhysicsServer3D::BODY_MODE_KINEMATIC) {
+			kin_body.push_back((int)body_r.size());
+			kin_xf0.push_back(xf_from(b.xf));
+			kin_lin.push_back(Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
+			kin_wy.push_back(b.angvel[1]);
+		} else {
+			ps->body_set_state(body, PhysicsServer3D::BODY_STATE_LINEAR_VELOCITY, Vector3(b.linvel[0], b.linvel[1], b.linvel[2]));
+			ps->body_set_state(body, PhysicsServer3D::BODY_STATE_ANGULAR_VELOCITY, Vector3(b.angvel[0], b.angvel[1], b.angvel[2]));
+		}
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, (b.flags & 1) != 0);
 		if (b.flags & 2) {
 			ps->body_set_enable_continuous_collision_detection(body, true);
@@ -417,6 +434,16 @@ int main(int argc, char **argv) {
 				case 10: ps->body_reset_mass_properties(body); break;
 				case 11: ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_MASS, e.v[0]); break;
 			}
+		}
+		for (size_t k = 0; k < kin_body.size(); k++) {
+			if (freed[kin_body[k]]) {
+				continue;
+			}
+			real_t t = (real_t)s * hd.dt;
+			Transform3D x;
+			x.basis = Basis(Vector3(0, 1, 0), kin_wy[k] * t) * kin_xf0[k].basis;
+			x.origin = kin_xf0[k].origin + kin_lin[k] * t;
+			ps->body_set_state(body_r[kin_body[k]], PhysicsServer3D::BODY_STATE_TRANSFORM, x);
 		}
 		ps->end_sync();
 		push();

@@ -185,6 +185,10 @@ enum { BPC_STATE_TRANSFORM = 0, BPC_STATE_LINEAR_VELOCITY = 1, BPC_STATE_ANGULAR
 int bpc_bodies_set_state(bpc_context *ctx, int state, const int32_t *slots, int n, const float *values);
 /* Gather / scatter variants of the bulk I/O for a list of bodies (state sync of the active bodies only, forces of the pushed
  * bodies only): one staging copy and one kernel whatever n is. */
+/* Two body records that are shapes of ONE object (the engine module's records for the further shapes of a static or kinematic
+ * body): they never enter the pair list -- in the reference the shapes of one body are not paired with each other
+ * (the pair test of its broadphase, `p_a == p_b`), whereas two separate kinematic bodies are.  same = 0 takes the mark back. */
+int bpc_bodies_set_same_object(bpc_context *ctx, int body_a, int body_b, int same);
 /* body_set_param(BODY_PARAM_INERTIA / BODY_PARAM_CENTER_OF_MASS) and body_reset_mass_properties (P3D/bradot_body_3d.cpp:209-229,
  * update_mass_properties :56-150): a body's own principal inertia and / or local centre of mass in place of the values
  * computed from its shape.  inertia: n x 3 or NULL (left as it is); all three components > 0 = the body's inertia about

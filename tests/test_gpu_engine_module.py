@@ -185,6 +185,64 @@ def test_engine_module_custom_inertia_and_centre_of_mass(tmp_path):
     assert np.max(np.abs(ref - plain[("bodies", steps)][:, 9:12])) > 0.02
 
 
+def test_kinematic_body_with_several_shapes(tmp_path):
+    """A kinematic platform of three shapes (slab and two rails) carrying boxes and spheres: (1) the C ABI moving three kinematic
+    records alike, marked as one object (bpc_bodies_set_same_object: they overlap, and two kinematic records would pair),
+    teacher-forced against the reference moving ONE kinematic body of three shapes (its targets: dump "kin_targets"): same
+    pair list per shape, state 5e-4 (the bar of test_kinematic_platform_matches_the_reference: acosf); (2) the module
+    (body_add_shape on a kinematic body, body_set_state(TRANSFORM) before every step) free-running beside the reference:
+    positions to 5 mm after 100 steps."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    if not parity.have_oracle():
+        pytest.skip("oracle/_ref/oracle_step not built")
+    sc = scenes.kinematic_platform(rails=True)
+    steps = 100
+    _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1)
+    further = [int(f) for f in np.nonzero(sc.bodies["flags"] & scenes.BODY_FURTHER_SHAPE)[0]]
+    owner = {}
+    for f in further:
+        o = f - 1
+        while o in owner:
+            o = owner[o]
+        owner[f] = o
+    ps = parity.new_server(sc, dump)
+    records = {}
+    for f, o in owner.items():
+        records.setdefault(o, [o]).append(f)
+    for recs in records.values():
+        for i in range(len(recs)):
+            for j in range(i + 1, len(recs)):
+                ps.bodies_set_same_object(recs[i], recs[j])
+    errs, collided = [], 0
+    for k in range(1, steps - 1):
+        parity.load_state(ps, dump, k)
+        for row in dump[("kin_targets", k + 1)]:
+            for b in records.get(int(row[0]), [int(row[0])]):
+                ps.bodies_write(server.FIELD_KINEMATIC_TARGET, row[1:13].reshape(1, 12), first=b)
+        ps.set_solve_order(parity.solve_order(dump, k + 1))
+        ps.step(sc.dt)
+        ref = dump[("bodies", k + 1)]
+        st = ps.bodies_read_state()
+        errs.append(float(np.max(np.abs(st[:, 0:18] - ref[:, 0:18]))))
+        ids, _, _ = ps.pairs_read()
+        rids, _, _ = parity.oracle_pairs(dump, k + 1)
+        order = np.argsort(parity.pair_keys(rids))
+        assert np.array_equal(parity.pair_keys(ids), parity.pair_keys(rids)[order]), k + 1
+        collided += int((ids[:, 3] & 1).sum())
+    ps.finish()
+    errs = np.array(errs)
+    assert collided > 300 and np.median(errs) < 1e-6 and errs.max() < 5e-4, (collided, float(np.median(errs)), float(errs.max()))
+    path = str(tmp_path / "scene.bscn")
+    sc.write(path)
+    r = subprocess.run([DEMO, path, str(steps), "--drive-kinematic"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    engine = np.array(json.loads(r.stdout.strip().splitlines()[-1])["origins"], np.float32)
+    ref = dump[("bodies", steps)][:, 9:12]
+    assert np.max(np.abs(engine - ref)) < 5e-3, float(np.abs(engine - ref).max())
+    assert ref[1, 0] > 0.9          # the platform did travel
+
+
 def test_engine_module_areas_of_several_shapes(tmp_path):
     """area_add_shape beyond the first through the RID API: the module keeps each further shape as an area record of its own that
     shares the area's group (one override per body, events per shape through the area's own callback).  scenes.area_groups()
