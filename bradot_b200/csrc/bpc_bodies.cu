@@ -89,7 +89,7 @@ static void mass_properties(const ShapeRec &sh, const bpc_body_desc &d, BodyProp
     if (d.mode == MODE_RIGID) {
         M3 sb(V3(d.shape_xf[0], d.shape_xf[1], d.shape_xf[2]), V3(d.shape_xf[3], d.shape_xf[4], d.shape_xf[5]), V3(d.shape_xf[6], d.shape_xf[7], d.shape_xf[8]));
         V3 so(d.shape_xf[9], d.shape_xf[10], d.shape_xf[11]);
-        float area = shape_volume(sh);
+        float area = (d.flags & 0x8000u) ? 0.f : shape_volume(sh); // a disabled shape takes no part in the mass data (is_shape_disabled, :63-65, :99-101)
         float total_area = 0.f;
         total_area += area;
         V3 com;
@@ -294,7 +294,10 @@ static int write_body_slots(bpc_context *ctx, const uint32_t *slots, const bpc_b
         bool ident = true;
         for (int q = 0; q < 12; q++) ident = ident && d.shape_xf[q] == ((q == 0 || q == 4 || q == 8) ? 1.f : 0.f);
         if (ident) flags |= BF_SHAPE_IDENT;
-        meta[i] = make_uint4(d.mode | (flags << 8) | (sh.meta.x << 24), d.layer, d.mask, d.space);
+        // body_set_shape_disabled: the shape leaves the broadphase (bradot_collision_object_3d.cpp:69-96) -- nothing pairs with it,
+        // no area or query sees it: no layer, no mask
+        const bool shape_off = (d.flags & 0x8000u) != 0u;
+        meta[i] = make_uint4(d.mode | (flags << 8) | (sh.meta.x << 24), shape_off ? 0u : d.layer, shape_off ? 0u : d.mask, d.space);
         sp[i] = sh.p;
         ctx->shape_type_mask |= 1u << sh.meta.x;
         if (sh.meta.x >= SH_CONVEX) memcpy(&sp[i].x, &sh.meta.y, 4);

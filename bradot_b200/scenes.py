@@ -47,6 +47,7 @@ HINGE_DEFAULTS = np.array([0.3, -np.pi, np.pi, 0.3, 0.9, 1.0, 0.0, 0.0], np.floa
 # bits 16..23: body_set_max_contacts_reported
 BODY_LIN_DAMP_REPLACE, BODY_ANG_DAMP_REPLACE, BODY_LOCK_SHIFT, BODY_REPORT_SHIFT = 16, 32, 8, 16
 BODY_NOT_PICKABLE = 128   # bit7: body_set_ray_pickable(false)
+BODY_SHAPE_DISABLED = 0x8000   # bit15: body_set_shape_disabled(body, 0, true)
 IDENT12 = np.array([1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0], dtype=np.float32)
 
 

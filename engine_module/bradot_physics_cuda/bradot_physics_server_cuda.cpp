@@ -553,7 +553,7 @@ void BradotPhysicsServerCUDA::_fill_desc(const Body *p_body, bpc_body_desc &r_de
 	r_desc.mode = (uint32_t)b->mode;
 	r_desc.shape = shape ? _shape_handle(shape) : 0;
 	r_desc.flags = (b->can_sleep ? 1 : 0) | (b->ccd ? 2 : 0) | (b->lin_damp_replace ? 16 : 0) | (b->ang_damp_replace ? 32 : 0) |
-			(b->omit_force_integration ? 64 : 0) | (b->ray_pickable ? 0 : 128) | ((b->locked_axis & 63) << 8);
+			(b->omit_force_integration ? 64 : 0) | (b->ray_pickable ? 0 : 128) | ((b->locked_axis & 63) << 8) | (p_body->shape_disabled ? 0x8000 : 0);
 	_xf_to_floats(b->xf, r_desc.xf);
 	_xf_to_floats(p_body->shape_xf, r_desc.shape_xf);
 	r_desc.linvel[0] = b->linvel.x; r_desc.linvel[1] = b->linvel.y; r_desc.linvel[2] = b->linvel.z;
@@ -686,7 +686,6 @@ void BradotPhysicsServerCUDA::body_add_shape(RID p_body, RID p_shape, const Tran
 	Body *body = body_owner.get_or_null(p_body);
 	ERR_FAIL_NULL(body);
 	ERR_FAIL_NULL(shape_owner.get_or_null(p_shape));
-	ERR_FAIL_COND_MSG(p_disabled, "BradotPhysicsCUDA: disabled shapes are not supported yet.");
 	if (body->shape.is_valid()) { // a further shape: bodies without dynamics only (static, kinematic), as a record of its own
 		ERR_FAIL_COND_MSG(body->mode > BODY_MODE_KINEMATIC, "BradotPhysicsCUDA: only static and kinematic bodies can have several shapes in this version.");
 		Body *part = memnew(Body);
@@ -696,6 +695,7 @@ void BradotPhysicsServerCUDA::body_add_shape(RID p_body, RID p_shape, const Tran
 		part->space = body->space;
 		part->shape = p_shape;
 		part->shape_xf = p_transform;
+		part->shape_disabled = p_disabled;
 		part->shape_index = body->parts.size() + 1;
 		body->parts.push_back(part);
 		if (body->space.is_valid()) {
@@ -706,7 +706,18 @@ void BradotPhysicsServerCUDA::body_add_shape(RID p_body, RID p_shape, const Tran
 	}
 	body->shape = p_shape;
 	body->shape_xf = p_transform;
+	body->shape_disabled = p_disabled;
 	_body_changed(body);
+}
+
+// body_set_shape_disabled (bradot_collision_object_3d.cpp:69-96): the shape leaves the broadphase and the mass data; the record stays
+void BradotPhysicsServerCUDA::body_set_shape_disabled(RID p_body, int p_shape_idx, bool p_disabled) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	Body *rec = _body_shape_record(body, p_shape_idx);
+	ERR_FAIL_NULL(rec);
+	rec->shape_disabled = p_disabled;
+	_body_changed(rec);
 }
 
 void BradotPhysicsServerCUDA::body_set_shape(RID p_body, int p_shape_idx, RID p_shape) {
@@ -759,6 +770,7 @@ void BradotPhysicsServerCUDA::body_remove_shape(RID p_body, int p_shape_idx) {
 		Body *dst = _body_shape_record(body, i), *src = body->parts[i];
 		dst->shape = src->shape;
 		dst->shape_xf = src->shape_xf;
+		dst->shape_disabled = src->shape_disabled;
 		_body_changed(dst);
 	}
 	_body_drop_part(body->parts[body->parts.size() - 1]);

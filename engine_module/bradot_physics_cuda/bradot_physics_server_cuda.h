@@ -125,6 +125,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 	struct Body {
 		RID self, space, shape;
 		Transform3D shape_xf;
+		bool shape_disabled = false;
 		BodyMode mode = BODY_MODE_RIGID;
 		Transform3D xf;
 		Vector3 linvel, angvel;
@@ -305,6 +306,7 @@ public:
 	virtual void shape_set_margin(RID p_shape, real_t p_margin) override;
 	virtual real_t shape_get_margin(RID p_shape) const override;
 	virtual void body_set_ray_pickable(RID p_body, bool p_enable) override;
+	virtual void body_set_shape_disabled(RID p_body, int p_shape_idx, bool p_disabled) override;
 	virtual void body_set_user_flags(RID p_body, uint32_t p_flags) override;
 	virtual uint32_t body_get_user_flags(RID p_body) const override;
 	virtual void body_set_contacts_reported_depth_threshold(RID p_body, real_t p_threshold) override;

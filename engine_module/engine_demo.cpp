@@ -264,6 +264,12 @@ int main(int argc, char **argv) {
 		if (b.flags & 2) {
 			ps->body_set_enable_continuous_collision_detection(body, true);
 		}
+		if (b.flags & 0x8000) {
+			ps->body_set_shape_disabled(body, 0, true);
+		}
+		if (b.flags & 128) {
+			ps->body_set_ray_pickable(body, false);
+		}
 		if (b.flags & 16) {
 			ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_LINEAR_DAMP_MODE, PhysicsServer3D::BODY_DAMP_MODE_REPLACE);
 		}

@@ -33,7 +33,8 @@ enum { BPC_JOINT_PIN = 0, BPC_JOINT_HINGE = 1, BPC_JOINT_CONE_TWIST = 2, BPC_JOI
 typedef struct bpc_body_desc {
     /* flags: bit0 can_sleep, bit1 continuous collision detection, bit2 start asleep, bit4 / bit5 linear / angular damp mode
      * REPLACE (BODY_PARAM_*_DAMP_MODE, P3D/bradot_body_3d.cpp:586-606), bit6 omit force integration, bit7 NOT ray pickable
-     * (body_set_ray_pickable(false); only rays cast with BPC_RAY_PICK care), bits 8..13 axis locks
+     * (body_set_ray_pickable(false); only rays cast with BPC_RAY_PICK care), bit15 the shape is disabled (body_set_shape_disabled:
+     * nothing collides with the body, no area or query sees it, and its mass data are those of a body without shapes), bits 8..13 axis locks
      * in PhysicsServer3D::BodyAxis order (body_set_axis_lock, P3D/bradot_body_3d.cpp:685-699).
      * bit2 is kept as given: the body sleeps until something wakes it.  (The reference would wake it on its first step:
      * every body whose shapes were just added has a pending shape update, and BradotBody3D::_shapes_changed ends in

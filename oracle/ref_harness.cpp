@@ -273,6 +273,12 @@ static void dump_step(Dump &d, World &w, int step) {
 		put3(items, s.aabb_cache.size);
 		BradotSpace3D *space = b->get_space();
 		BradotBroadPhase3DBVH *bp = static_cast<BradotBroadPhase3DBVH *>(space->get_broadphase());
+		if (s.bpid == 0) { // a disabled shape is in no broadphase
+			for (int q = 0; q < 8; q++) {
+				items.push_back(0.f);
+			}
+			continue;
+		}
 		uint32_t id = s.bpid - 1;
 		BVHHandle h;
 		h.set_id(id);
@@ -1079,6 +1085,9 @@ int main(int argc, char **argv) {
 		ps->body_set_state(body, PhysicsServer3D::BODY_STATE_CAN_SLEEP, (b.flags & 1) != 0);
 		if (b.flags & 2) {
 			ps->body_set_enable_continuous_collision_detection(body, true);
+		}
+		if (b.flags & 0x8000) { // bit15: the shape is disabled
+			ps->body_set_shape_disabled(body, 0, true);
 		}
 		if (b.flags & 128) { // bit7: not ray pickable
 			ps->body_set_ray_pickable(body, false);

@@ -76,7 +76,14 @@ def test_engine_module_matches_direct_c_abi(tmp_path):
     assert st["contact_pairs"] > 0
 
 
-@pytest.mark.parametrize("name", ["pushed", "bullets", "terrain", "cone_twist", "slider", "sixdof"])
+def _pile_with_disabled_shapes():
+    sc = scenes.mixed_pile(4, half=3.0)
+    dyn = np.nonzero(sc.bodies["mode"] == scenes.MODE_RIGID)[0]
+    sc.bodies["flags"][dyn[::3]] |= scenes.BODY_SHAPE_DISABLED
+    return sc
+
+
+@pytest.mark.parametrize("name", ["pushed", "bullets", "terrain", "cone_twist", "slider", "sixdof", "disabled"])
 def test_engine_module_forces_and_ccd_match_direct_c_abi(tmp_path, name):
     """body_apply_central_force / body_apply_torque and body_set_enable_continuous_collision_detection through the RID API
     against the same scene driven through the C ABI directly (force rows written before every step; CCD from the flags)."""
@@ -85,6 +92,7 @@ def test_engine_module_forces_and_ccd_match_direct_c_abi(tmp_path, name):
     sc = {"pushed": scenes.pushed, "bullets": scenes.bullets, "terrain": scenes.terrain_pile,    # terrain: a ConcavePolygonShape3D
           "cone_twist": lambda: scenes.hanging_chains(cone_twist=True),                          # joint_make_cone_twist / cone_twist_joint_set_param
           "sixdof": scenes.sixdof_rigs,                                                           # joint_make_generic_6dof / generic_6dof_joint_set_param / _set_flag
+          "disabled": lambda: _pile_with_disabled_shapes(),                                       # body_set_shape_disabled
           "slider": scenes.slider_rigs}[name]()                                                   # joint_make_slider / slider_joint_set_param
     path = str(tmp_path / "scene.bscn")
     sc.write(path)

@@ -156,6 +156,42 @@ def _apply_events(ps, events, step, freed):
             ps.body_set_state([body], server.BODY_STATE_CAN_SLEEP, v[:1])
 
 
+def test_disabled_shapes_follow_the_reference():
+    """body_set_shape_disabled (bradot_collision_object_3d.cpp:69-96; update_mass_properties skips the shape, bradot_body_3d.cpp:63-65):
+    every third body of a settling pile has its shape disabled -- it falls through the others and through the floor, pairs
+    with nothing, is seen by no ray.  Free-running: neither pair list holds such a body, positions of the disabled bodies (pure free fall) agree to 1e-4, the pile's to 2 mm early on."""
+    _need_oracle()
+    sc = scenes.mixed_pile(4, half=3.0)
+    dyn = np.nonzero(sc.bodies["mode"] == scenes.MODE_RIGID)[0]
+    off = dyn[::3]
+    sc.bodies["flags"][off] |= scenes.BODY_SHAPE_DISABLED
+    steps = 60
+    rays = np.zeros((len(off), 6), np.float32)
+    _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1)
+    ps = parity.new_server(sc, dump)
+    for k in range(1, steps + 1):
+        ps.step(sc.dt)
+        st = ps.bodies_read_state()
+        ref = dump[("bodies", k)]
+        assert np.max(np.abs(st[off, 0:18] - ref[off, 0:18])) < 1e-4, k
+        if k <= 25:
+            assert np.max(np.abs(st[:, 9:12] - ref[:, 9:12])) < 2e-3, k
+        if k in (10, 25):       # (not the first step: the reference re-stores every box before its first pairing, DESIGN.md known deviations)
+            ids, _, _ = ps.pairs_read()
+            rids, _, _ = parity.oracle_pairs(dump, k)
+            assert not np.isin(ids[:, 0:2], off).any() and not np.isin(rids[:, 0:2], off).any()
+            # (the lists themselves are not compared in a free run: speculative box-only pairs may appear a step apart, DESIGN.md)
+            assert abs(len(ids) - len(rids)) <= len(rids) // 10
+    assert np.all(st[off, 10] < -0.4) and np.mean(st[np.setdiff1d(dyn, off), 10] > 0.0) > 0.9      # through the floor / on it
+    rays[:, 0:3] = st[off, 9:12] + np.array([0, 1.0, 0], np.float32)
+    rays[:, 3:6] = st[off, 9:12] - np.array([0, 1.0, 0], np.float32)
+    hit, body, _, _ = ps.intersect_rays(rays)
+    assert not np.isin(body[hit], off).any()
+    mp = ps.bodies_read(server.FIELD_MASS_PROPS)
+    assert np.allclose(mp[off, 1:4], 1.0) and np.allclose(mp[off, 4:7], 0.0)          # a body without shapes: unit inertia, centre of mass at the origin
+    ps.finish()
+
+
 def test_custom_inertia_and_centre_of_mass_follow_the_reference():
     """body_set_param(BODY_PARAM_INERTIA / BODY_PARAM_CENTER_OF_MASS) and body_reset_mass_properties (bradot_body_3d.cpp:168-172,
     209-229, update_mass_properties :56-150): tumbling bodies dropped on a plane get, at step 2, a full custom inertia, a
