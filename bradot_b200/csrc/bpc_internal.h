@@ -484,6 +484,7 @@ int bpc_rebuild_lists(bpc_context *ctx);
 int bpc_resolve_step(bpc_context *ctx);
 int bpc_launch_broadphase(bpc_context *ctx);
 int bpc_build_tree(bpc_context *ctx); // LBVH over the current stored boxes (also used by the space queries)
+int bpc_flush_tables(bpc_context *ctx); // bpc_api.cu: shapes, joints, exceptions, spaces to the device when they changed
 int bpc_launch_islands(bpc_context *ctx);
 int bpc_launch_narrowphase(bpc_context *ctx);
 int bpc_flush_area_tables(bpc_context *ctx);                                      // k_areas.cu

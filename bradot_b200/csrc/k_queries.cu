@@ -322,6 +322,66 @@ static void q_fill(bpc_context *ctx, QArgs &a, int space, int n, unsigned mask, 
     if (ctx->h_areas.empty()) a.flags &= ~(uint32_t)BPC_QUERY_AREAS; // no area was ever made: nothing to walk
 }
 
+// PhysicsDirectSpaceState3D::get_closest_point_to_object_volume (bradot_space_3d.cpp:573-611) for body records: the point of the
+// body's shape nearest to a world point (the point itself when inside)
+__global__ void __launch_bounds__(Q_THREADS) k_closest_points(uint32_t n, const int32_t *__restrict__ bodies, const float *__restrict__ points, float *__restrict__ out,
+                                                              QArgs a, const uint4 *__restrict__ edges) {
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    uint32_t j = (uint32_t)bodies[r];
+    V3 p(points[r * 3 + 0], points[r * 3 + 1], points[r * 3 + 2]);
+    uint4 m = a.meta[j];
+    BodyXf bx = a.xf[j];
+    X3 xf(M3(f4v(bx.r0), f4v(bx.r1), f4v(bx.r2)), f4v(bx.o));
+    if (!((m.x >> 8) & BF_SHAPE_IDENT)) {
+        BodyXf sx = a.shape_xf[j];
+        xf = xf * X3(M3(f4v(sx.r0), f4v(sx.r1), f4v(sx.r2)), f4v(sx.o));
+    }
+    QShape s;
+    s.type = m.x >> 24;
+    s.p = a.shape_p[j];
+    if (s.type >= SH_CONVEX) s.mesh = a.pools.meshes[__float_as_uint(s.p.x)];
+    V3 c = xform(xf, q_shape_closest_point(a.pools, edges, s, xform(affine_inverse(xf), p)));
+    out[r * 3 + 0] = c.x;
+    out[r * 3 + 1] = c.y;
+    out[r * 3 + 2] = c.z;
+}
+
+extern "C" int bpc_bodies_closest_points(bpc_context *ctx, int n, const int32_t *bodies, const float *points, float *out) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && (!bodies || !points || !out))) {
+        ctx->err = "bpc_bodies_closest_points: bad arguments";
+        return -1;
+    }
+    for (int i = 0; i < n; i++) {
+        if (bodies[i] < 0 || (uint32_t)bodies[i] >= ctx->n_bodies || ctx->h_dead[bodies[i]]) {
+            ctx->err = "bpc_bodies_closest_points: invalid body";
+            return -1;
+        }
+    }
+    if (n == 0) return 0;
+    BPC_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (bpc_flush_tables(ctx)) return -1;
+    size_t id_words = ((size_t)n + 3) & ~(size_t)3, pt_words = ((size_t)n * 3 + 3) & ~(size_t)3;
+    ctx->staging.reserve(id_words + pt_words * 2 + 16, false, st);
+    if (!ctx->staging.p) {
+        ctx->err = "bpc_bodies_closest_points: out of device memory";
+        return -1;
+    }
+    int32_t *d_ids = (int32_t *)ctx->staging.p;
+    float *d_in = ctx->staging.p + id_words, *d_out = d_in + pt_words;
+    BPC_CHECK(cudaMemcpyAsync(d_ids, bodies, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    BPC_CHECK(cudaMemcpyAsync(d_in, points, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+    QArgs a;
+    q_fill(ctx, a, 0, n, 0xffffffffu, 0);
+    k_closest_points<<<(n + Q_THREADS - 1) / Q_THREADS, Q_THREADS, 0, st>>>((uint32_t)n, d_ids, d_in, d_out, a, ctx->medges.p);
+    BPC_CHECK(cudaGetLastError());
+    BPC_CHECK(cudaMemcpyAsync(out, d_out, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    BPC_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}
+
 // ShapeParameters / RayParameters / PointParameters ::exclude (servers/physics_server_3d.h:139-201): the bodies every query of
 // this context skips from now on; n = 0 clears the list.
 extern "C" int bpc_space_set_query_exclude(bpc_context *ctx, const int32_t *bodies, int n) {

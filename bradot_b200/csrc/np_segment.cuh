@@ -188,6 +188,99 @@ __device__ inline bool q_shape_point_inside(const MeshPools &a, const QShape &s,
     }
 }
 
+// BradotShape3D::get_closest_point_to of the plane, sphere, box, capsule and convex polygon (bradot_shape_3d.cpp:142-148, 287-294,
+// 431-478, 621-633, 1030-1086): the point itself when it is inside, else the nearest point of the surface; triangle meshes
+// and height maps answer the origin (:1429-1431, :2011-2013).  `edges`: the hull edge pool (vertex a, vertex b, ...).
+__device__ inline V3 q_shape_closest_point(const MeshPools &a, const uint4 *edges, const QShape &s, V3 p) {
+    switch (s.type) {
+        case SH_PLANE: {
+            V3 n(s.p.x, s.p.y, s.p.z);
+            if (dot(n, p) > s.p.w) return p - n * (dot(n, p) - s.p.w); // is_point_over -> project
+            return p;
+        }
+        case SH_SPHERE: {
+            float l = length(p);
+            if (l < s.p.x) return p;
+            return (p / l) * s.p.x;
+        }
+        case SH_BOX: {
+            const V3 he(s.p.x, s.p.y, s.p.z);
+            int outside = 0;
+            V3 min_point;
+            for (int i = 0; i < 3; i++) {
+                if (fabsf(comp(p, i)) > comp(he, i)) {
+                    outside++;
+                    if (outside == 1) { // the face plane of that axis
+                        V3 n;
+                        float c = comp(p, i);
+                        set_comp(n, i, c > 0.f ? 1.f : (c < 0.f ? -1.f : 0.f));
+                        min_point = p - n * (dot(n, p) - comp(he, i));
+                    }
+                }
+            }
+            if (!outside) return p;
+            if (outside == 1) return min_point;
+            // beyond two or three faces: the three edges that meet at the nearest corner
+            auto sgn = [](float v) { return v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f); };
+            const V3 corner(he.x * sgn(p.x), he.y * sgn(p.y), he.z * sgn(p.z));
+            float min_distance = 1e20f;
+            for (int i = 0; i < 3; i++) {
+                V3 other = corner;
+                set_comp(other, i, -comp(other, i));
+                V3 e = closest_point_to_segment(p, corner, other);
+                float d = length(p - e);
+                if (d < min_distance) {
+                    min_point = e;
+                    min_distance = d;
+                }
+            }
+            return min_point;
+        }
+        case SH_CAPSULE: {
+            const float radius = s.p.x, height = s.p.y;
+            V3 q = closest_point_to_segment(p, V3(0.f, -height * 0.5f + radius, 0.f), V3(0.f, height * 0.5f - radius, 0.f));
+            if (length(q - p) < radius) return p;
+            return q + normalized(p - q) * radius;
+        }
+        case SH_CONVEX: {
+            bool all_inside = true;
+            for (uint32_t i = 0; i < s.mesh.face_cnt; i++) {
+                float4 pl = a.mplanes[s.mesh.face_ofs + i];
+                V3 fn(pl.x, pl.y, pl.z);
+                if (!(dot(fn, p) > pl.w)) continue;
+                all_inside = false;
+                bool is_inside = true;
+                uint2 f = a.mfaces[s.mesh.face_ofs + i];
+                for (uint32_t j = 0; j < f.y; j++) {
+                    V3 va = f4v(a.mverts[s.mesh.vert_ofs + a.mindex[f.x + j]]);
+                    V3 vb = f4v(a.mverts[s.mesh.vert_ofs + a.mindex[f.x + (j + 1) % f.y]]);
+                    V3 n = normalized(cross(va - vb, fn));
+                    if (dot(n, p) > dot(n, va)) { // Plane(n, a).is_point_over
+                        is_inside = false;
+                        break;
+                    }
+                }
+                if (is_inside) return p - fn * (dot(fn, p) - pl.w);
+            }
+            if (all_inside) return p;
+            float min_distance = 1e20f;
+            V3 min_point;
+            for (uint32_t i = 0; i < s.mesh.edge_cnt; i++) {
+                uint4 e = edges[s.mesh.edge_ofs + i];
+                V3 c = closest_point_to_segment(p, f4v(a.mverts[s.mesh.vert_ofs + e.x]), f4v(a.mverts[s.mesh.vert_ofs + e.y]));
+                float d = length(c - p);
+                if (d < min_distance) {
+                    min_distance = d;
+                    min_point = c;
+                }
+            }
+            return min_point;
+        }
+        default:
+            return V3();
+    }
+}
+
 // BradotConcavePolygonShape3D::intersect_segment / _cull_segment + BradotFaceShape3D::intersect_segment
 // (bradot_shape_3d.cpp:1350-1423, 1257-1271): the nearest face the segment crosses, front faces only unless the mesh collides
 // on both sides and the query asks for back faces.  Mesh layout: np_face.cuh.

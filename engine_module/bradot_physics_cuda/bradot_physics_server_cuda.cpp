@@ -304,6 +304,48 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 	return hits;
 }
 
+// get_closest_point_to_object_volume (bradot_space_3d.cpp:573-611) of a body: every record of the body (its shapes) is asked in one
+// bpc_bodies_closest_points, the nearest answer wins; a body without shapes answers its origin.  Areas are not bodies on
+// the GPU side and are not answered here.
+Vector3 BradotPhysicsDirectSpaceStateCUDA::get_closest_point_to_object_volume(RID p_object, const Vector3 p_point) const {
+	ERR_FAIL_NULL_V(server, Vector3());
+	BradotPhysicsServerCUDA::Body *body = server->body_owner.get_or_null(p_object);
+	ERR_FAIL_NULL_V_MSG(body, Vector3(), "BradotPhysicsCUDA: get_closest_point_to_object_volume answers for bodies only.");
+	server->_flush_pending();
+	LocalVector<int32_t> slots;
+	if (body->slot >= 0 && !body->shape_disabled) {
+		slots.push_back(body->slot);
+	}
+	for (const BradotPhysicsServerCUDA::Body *part : body->parts) {
+		if (part->slot >= 0 && !part->shape_disabled) {
+			slots.push_back(part->slot);
+		}
+	}
+	if (slots.is_empty()) {
+		return Transform3D(server->body_get_state(p_object, PhysicsServer3D::BODY_STATE_TRANSFORM)).origin;
+	}
+	LocalVector<float> pts, out;
+	pts.resize(slots.size() * 3);
+	out.resize(slots.size() * 3);
+	for (uint32_t i = 0; i < slots.size(); i++) {
+		pts[i * 3 + 0] = p_point.x;
+		pts[i * 3 + 1] = p_point.y;
+		pts[i * 3 + 2] = p_point.z;
+	}
+	ERR_FAIL_COND_V_MSG(bpc_bodies_closest_points(server->ctx, (int)slots.size(), slots.ptr(), pts.ptr(), out.ptr()) < 0, Vector3(), bpc_last_error(server->ctx));
+	real_t min_distance = 1e20;
+	Vector3 min_point;
+	for (uint32_t i = 0; i < slots.size(); i++) {
+		Vector3 c(out[i * 3 + 0], out[i * 3 + 1], out[i * 3 + 2]);
+		real_t d = c.distance_to(p_point);
+		if (d < min_distance) {
+			min_distance = d;
+			min_point = c;
+		}
+	}
+	return min_point;
+}
+
 int BradotPhysicsDirectSpaceStateCUDA::intersect_point(const PointParameters &p_parameters, ShapeResult *r_results, int p_result_max) {
 	ERR_FAIL_NULL_V(server, 0);
 	if (p_result_max <= 0 || (!p_parameters.collide_with_bodies && !p_parameters.collide_with_areas)) {

@@ -42,7 +42,7 @@ public:
 	virtual bool collide_shape(const ShapeParameters &p_parameters, Vector3 *r_results, int p_result_max, int &r_result_count) override;
 	virtual bool rest_info(const ShapeParameters &p_parameters, ShapeRestInfo *r_info) override;
 	void _fill_rest_info(const bpc_rest_info &p_info, ShapeRestInfo *r_info) const;
-	virtual Vector3 get_closest_point_to_object_volume(RID p_object, const Vector3 p_point) const override { BPC_UNSUPPORTED("get_closest_point_to_object_volume"); return p_point; }
+	virtual Vector3 get_closest_point_to_object_volume(RID p_object, const Vector3 p_point) const override;
 };
 
 // PhysicsDirectBodyState3D of one body (servers/physics_server_3d.h:46-115; reference implementation

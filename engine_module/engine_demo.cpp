@@ -517,6 +517,13 @@ int main(int argc, char **argv) {
 		}
 		printf("%s[%d, %d, %.9g, %.9g, %.9g]", i ? ", " : "", hit ? 1 : 0, idx, hit ? rr.position.x : 0.0, hit ? rr.position.y : 0.0, hit ? rr.position.z : 0.0);
 	}
+	// get_closest_point_to_object_volume through the RID API: a point beside each of the first bodies
+	printf("], \"closest\": [");
+	for (int i = 0; ds && i < n_rays; i++) {
+		Transform3D t = freed[i] ? Transform3D() : Transform3D(ps->body_get_state(body_r[i], PhysicsServer3D::BODY_STATE_TRANSFORM));
+		Vector3 c = freed[i] ? Vector3() : ds->get_closest_point_to_object_volume(body_r[i], t.origin + Vector3(0.6f, 0.4f, -0.3f));
+		printf("%s[%.9g, %.9g, %.9g]", i ? ", " : "", c.x, c.y, c.z);
+	}
 	// cast_motion and rest_info through the RID API: a sphere dropped from above each of the first bodies with that body excluded
 	// (so it lands on whatever lies under it), and the same sphere resting at the body's own place
 	printf("], \"area_events\": [");

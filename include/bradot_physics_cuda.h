@@ -357,6 +357,12 @@ int bpc_space_intersect_rays(bpc_context *ctx, int space, int n, const float *fr
 int bpc_space_intersect_points(bpc_context *ctx, int space, int n, const float *points, unsigned collision_mask, int flags,
                                int max_results, int32_t *out_counts, int32_t *out_bodies);
 
+/* PhysicsDirectSpaceState3D::get_closest_point_to_object_volume (servers/physics_server_3d.h:207; implementation
+ * modules/bradot_physics_3d/bradot_space_3d.cpp:573-611 with the shapes' get_closest_point_to), batched: for each (body record,
+ * world point) the point of the record's shape nearest to it -- the point itself when it is inside.  points / out: n x 3.
+ * (An object of several shapes is several records: the caller keeps the nearest answer, as the reference's loop does.) */
+int bpc_bodies_closest_points(bpc_context *ctx, int n, const int32_t *bodies, const float *points, float *out);
+
 /* PhysicsDirectSpaceState3D::intersect_shape (servers/physics_server_3d.h:183-205; implementation
  * modules/bradot_physics_3d/bradot_space_3d.cpp:208-262), batched: query i is shape handle shapes[i] (from bpc_shape_create*)
  * placed at xforms[i] (12 floats, basis rows + origin), grown by `margin` (0 = the plain routines, else the reference's withMargin

@@ -535,6 +535,20 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 		}
 	}
 	d.arr("points", step, "i4", { (uint64_t)n, 9 }, pts.data(), pts.size() * 4);
+	{ // get_closest_point_to_object_volume (bradot_space_3d.cpp:573-611): ray i's origin against body i % bodies
+		std::vector<float> cl(n * 3, 0.f);
+		for (size_t i = 0; i < n && ds; i++) {
+			size_t bi = i % w.bodies.size();
+			if (w.body_freed[bi]) {
+				continue;
+			}
+			Vector3 c = ds->get_closest_point_to_object_volume(w.bodies[bi], Vector3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]));
+			cl[i * 3 + 0] = c.x;
+			cl[i * 3 + 1] = c.y;
+			cl[i * 3 + 2] = c.z;
+		}
+		d.arr("closest", step, "f4", { (uint64_t)n, 3 }, cl.data(), cl.size() * 4);
+	}
 	if (!w.areas.empty()) { // "points_areas": the same with collide_with_areas, up to 16 results, areas as -2 - index
 		std::vector<int32_t> pa(n * 17, -1);
 		for (size_t i = 0; i < n; i++) {

@@ -54,6 +54,10 @@ def test_engine_module_matches_direct_c_abi(tmp_path):
         assert int(casts[i, 3]) == (rest["body"][0] if rest["hit"][0] else -1), i
         if rest["hit"][0]:
             assert np.array_equal(casts[i, 4:7].astype(np.float32), rest["point"][0])
+    # get_closest_point_to_object_volume through the RID API == bpc_bodies_closest_points on the same state
+    closest = np.array(out["closest"], np.float64).astype(np.float32)
+    mine_c = ps.bodies_closest_points(np.arange(n), direct[:n] + np.array([0.6, 0.4, -0.3], np.float32))
+    assert np.array_equal(closest, mine_c), float(np.abs(closest - mine_c).max())
     # body_test_motion through the RID API == bpc_bodies_test_motion on the same state
     mot = np.array(out["motions"], np.float64)
     prm = np.zeros(n, server.MOTION_PARAMS_DT)

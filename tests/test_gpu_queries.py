@@ -56,6 +56,33 @@ def test_intersect_rays_convex_hulls():
     assert _compare(sc, _rays(4000, 6, 4.0, 8.0), 50, [1, 25, 49]) > 2000
 
 
+@pytest.mark.parametrize("name", ["mixed", "hulls"])
+def test_closest_point_to_object_volume(name):
+    """PhysicsDirectSpaceState3D::get_closest_point_to_object_volume (bradot_space_3d.cpp:573-611; get_closest_point_to of the plane,
+    sphere, box, capsule and convex polygon): 3 000 (body, point) pairs per scene at three steps against the reference --
+    points inside a shape come back unchanged, the others land on the surface; to 1e-4."""
+    parity_needed()
+    sc = scenes.mixed_pile(5, half=3.5) if name == "mixed" else scenes.convex_pile(4)
+    rays = _rays(3000, 31, 3.6, 5.0)
+    nb = len(sc.bodies)
+    which = np.arange(len(rays)) % nb
+    rays[:400, 0:3] = sc.bodies["xf"][which[:400], 9:12] + np.float32(0.02)      # these start inside their body (at the first step at least)
+    _, dump = parity.run_oracle(sc, 40, dump_from=0, dump_every=1, rays=rays)
+    ps = parity.new_server(sc, dump)
+    unchanged = moved = 0
+    for k in (1, 20, 39):
+        parity.load_state(ps, dump, k)
+        mine = ps.bodies_closest_points(which, rays[:, 0:3])
+        ref = dump[("closest", k)]
+        err = np.abs(mine - ref).max(axis=1)
+        assert (err < 1e-4).mean() > 0.999 and np.median(err) < 1e-6, (k, float(err.max()), int((err >= 1e-4).sum()))
+        same = np.all(ref == rays[:, 0:3], axis=1)
+        unchanged += int(same.sum())
+        moved += int((~same).sum())
+    ps.finish()
+    assert unchanged > 50 and moved > 5000
+
+
 def test_intersect_rays_pick_ray_passes_unpickable_bodies():
     """RayParameters::pick_ray with body_set_ray_pickable(false) on every third body (bradot_space_3d.cpp:134): those bodies are
     passed through by picking rays and hit by ordinary ones, as in the reference."""
