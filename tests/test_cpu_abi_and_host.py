@@ -72,6 +72,27 @@ def test_scene_file_roundtrip(tmp_path):
     assert scenes.BODY_DT.itemsize == 4 * 4 + 12 * 4 * 2 + 6 * 4 + 6 * 4 + 8   # must match bpc_body_desc / ScnBody
 
 
+def test_scene_file_carries_the_round_2_sections(tmp_path):
+    """Areas (with groups), long joint parameter rows, per-shape solver bias and the body flags added in round 2 survive a
+    write / read, the record sizes are those of the C ABI, and the generators place what their docstrings say."""
+    for sc in (scenes.slider_rigs(4), scenes.sixdof_rigs(4), scenes.area_groups(), scenes.level_geometry(2), scenes.kinematic_platform(rails=True)):
+        p = str(tmp_path / "s.bscn")
+        sc.write(p)
+        back = scenes.Scene.read(p)
+        for name in ("shapes", "bodies", "joints", "areas", "joint_ext"):
+            assert getattr(sc, name).tobytes() == getattr(back, name).tobytes(), (sc.name, name)
+    assert scenes.JOINT_DT.itemsize == 160 and scenes.AREA_DT.itemsize == 164 and scenes.JOINT_EXT_DT.itemsize == 128 and scenes.SHAPE_DT.itemsize == 32
+    six = scenes.sixdof_rigs(6)
+    assert (six.joints["type"] == scenes.JOINT_6DOF).all() and set(six.joint_ext["first"]) == {0, 28, 56} and (six.joint_ext["count"] == 28).all()
+    assert np.array_equal(scenes.g6dof_axis_defaults()[[2, 3, 4, 10, 11, 15, 18, 22]], np.array([0.7, 0.5, 1.0, -1e30, 1e30, 300.0, 0.1, 1.0], np.float32))
+    ag = scenes.area_groups()
+    assert list(ag.areas["group"]) == [1, 1, 0, 2, 2]
+    lv = scenes.level_geometry(2)
+    assert int(((lv.bodies["flags"] & scenes.BODY_FURTHER_SHAPE) != 0).sum()) == 5 and not (scenes.level_geometry(2, merged=False).bodies["flags"] & scenes.BODY_FURTHER_SHAPE).any()
+    ch = scenes.hanging_chains(3, 5, cone_twist=True)
+    assert (ch.joints["type"] == scenes.JOINT_CONE_TWIST).sum() == 6
+
+
 def test_scene_generators_are_deterministic_and_sized():
     a, b = scenes.mixed_pile(4), scenes.mixed_pile(4)
     assert a.bodies.tobytes() == b.bodies.tobytes() and a.shapes.tobytes() == b.shapes.tobytes()
