@@ -57,7 +57,7 @@ extern "C" void bpc_destroy(bpc_context *ctx) {
     }
     ctx->except_keys.free_(); ctx->con_list.free_(); ctx->con_color.free_(); ctx->con_sorted.free_(); ctx->con_sorted_alt.free_();
     ctx->con_info.free_(); ctx->con_bin.free_(); ctx->con_sorted_color.free_(); ctx->joint_color.free_(); ctx->report_cap.free_(); ctx->report_ofs.free_(); ctx->report_count.free_(); ctx->reports.free_(); ctx->report_overflow.free_(); ctx->report_overflow_body.free_(); ctx->con_cls.free_(); ctx->bin_tab.free_(); ctx->bin_base.free_(); ctx->body_best.free_(); ctx->body_colmask.free_(); ctx->color_start.free_(); ctx->scontacts.free_();
-    ctx->forced_order.free_(); ctx->forced_level_start.free_(); ctx->forced_keys.free_(); ctx->d_joints.free_(); ctx->d_jext.free_(); ctx->d_shape_bias.free_(); ctx->d_same.free_();
+    ctx->forced_order.free_(); ctx->forced_level_start.free_(); ctx->forced_keys.free_(); ctx->d_joints.free_(); ctx->d_jext.free_(); ctx->d_shape_bias.free_(); ctx->d_same.free_(); ctx->d_coll_priority.free_();
     ctx->async_staging.free_(); ctx->force_staging.free_();
     if (ctx->ev_h2d) cudaEventDestroy(ctx->ev_h2d);
     if (ctx->ev_unpacked) cudaEventDestroy(ctx->ev_unpacked);

@@ -528,6 +528,7 @@ extern "C" int bpc_bodies_destroy(bpc_context *ctx, const int32_t *slots, int n)
         }
         ctx->h_dead[i] = 1;
         ctx->h_mass_override.erase(i);
+        if (i < ctx->h_coll_priority.size()) ctx->h_coll_priority[i] = 1.0f;
         ctx->h_mode[i] = MODE_STATIC;
         ctx->h_big[i] = 0;
         ctx->h_ccd[i] = 0;
@@ -1119,6 +1120,18 @@ __global__ void k_scatter_forces(uint32_t n, const uint32_t *__restrict__ slots,
 
 // Pipelined read-back: the rows are packed on the main stream into a buffer of their own, the copy to the host runs on a side
 // stream, so the next step's kernels do not wait for the bus (nor the copy for them).
+extern "C" int bpc_bodies_set_collision_priority(bpc_context *ctx, const int32_t *slots, int n, const float *priorities) {
+    if (!ctx) return -1;
+    if (n < 0 || (n > 0 && (!slots || !priorities))) return fail(ctx, "bpc_bodies_set_collision_priority: bad arguments");
+    for (int i = 0; i < n; i++) {
+        if (slots[i] < 0 || (uint32_t)slots[i] >= ctx->n_bodies || ctx->h_dead[slots[i]]) return fail(ctx, "bpc_bodies_set_collision_priority: invalid body");
+        if (!(priorities[i] > 0.f)) return fail(ctx, "bpc_bodies_set_collision_priority: a priority must be positive");
+    }
+    ctx->h_coll_priority.resize(ctx->n_bodies, 1.0f);
+    for (int i = 0; i < n; i++) ctx->h_coll_priority[slots[i]] = priorities[i];
+    return 0;
+}
+
 extern "C" int bpc_bodies_set_same_object(bpc_context *ctx, int body_a, int body_b, int same) {
     if (!ctx) return -1;
     if (body_a < 0 || body_b < 0 || (uint32_t)body_a >= ctx->n_bodies || (uint32_t)body_b >= ctx->n_bodies || body_a == body_b || ctx->h_dead[body_a] || ctx->h_dead[body_b])

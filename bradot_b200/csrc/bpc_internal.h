@@ -254,6 +254,8 @@ struct bpc_context {
     std::vector<uint64_t> h_same; // sorted (a << 32 | b), a < b: records that are shapes of one object and never pair
     DevBuf<uint64_t> d_same;
     bool same_dirty = false;
+    std::vector<float> h_coll_priority; // body_set_collision_priority per body; empty until one is set (body_test_motion only)
+    DevBuf<float> d_coll_priority;
     std::vector<float> h_shape_bias; // shape_set_custom_solver_bias per shape; empty until one is set
     DevBuf<float> d_shape_bias;
     std::vector<float> h_jext; // JEXT_STRIDE values per joint, present once a joint with a long parameter table exists

@@ -776,6 +776,7 @@ struct MtArgs {
     const uint32_t *shape_id;
     const uint64_t *except_keys;
     uint32_t n_except, n_bodies;
+    const float *priority; // body_set_collision_priority per body, or null: every obstacle weighs 1
 };
 
 // _cull_aabb_for_body's filter (:619-649) on one candidate: not the body itself, its layer meets the body's mask, no
@@ -823,13 +824,17 @@ __device__ __noinline__ void mt_rest_contacts(const MtArgs *m, const QsArgs *a, 
 // (Both steps are functions of their own on purpose: inlined into the one large kernel, the plane routine was seen to read
 // another transform than the one handed to it -- a build-dependent effect that went away with the call boundary.)
 __device__ __noinline__ void mt_recover_contacts(const MtArgs *m, const QsArgs *a, uint32_t self, uint32_t self_mask, const Sh *bs, const X3 *bsx, V3 bmin,
-                                                 V3 bmax, float margin, RawSink *sink) {
+                                                 V3 bmax, float margin, RawSink *sink, float *prio) {
+    int told = 0;
     qs_for_candidates(*a, bmin, bmax, [&](uint32_t j) {
         Sh sb;
         X3 xb;
         if (!mt_body(*m, self, self_mask, j, sb, xb)) return;
         Manifold *none = nullptr;
         solve_static<false, true, true>(*bs, *bsx, sb, xb, *none, nullptr, sink, nullptr, margin, 0.f);
+        // the collision priority of the obstacle goes with every pair it ADDED (a pair that replaced a shallower one keeps
+        // the slot's old priority: bradot_space_3d.cpp:748-751)
+        while (told < sink->n) prio[told++] = m->priority ? m->priority[j] : 1.0f;
     });
 }
 
@@ -879,10 +884,14 @@ __global__ void __launch_bounds__(32) k_test_motion(MtArgs m) {
             V3 bmin, bmax;
             body_box(body_transform, margin + 1e-4f, bmin, bmax);
             const X3 bsx = body_transform * local;
-            mt_recover_contacts(&m, &a, self, ms.z, &bs, &bsx, bmin, bmax, margin, &sink);
+            float prio[MT_MAX_RECOVER];
+            mt_recover_contacts(&m, &a, self, ms.z, &bs, &bsx, bmin, bmax, margin, &sink, prio);
             if (sink.n == 0) break;
             recovered = true;
-            // every obstacle has collision priority 1 here, so the weights (priorities[i] * inv_total_weight) are all 1
+            // the obstacles' collision priorities weigh the push (:758-762); all 1 (no priority was ever set) makes the weight exactly 1
+            float inv_total_weight = 0.0f;
+            for (int i = 0; i < sink.n; i++) inv_total_weight += prio[i];
+            inv_total_weight = is_zero_approx(inv_total_weight) ? 1.0f : (float)sink.n / inv_total_weight;
             V3 recover_motion;
             for (int i = 0; i < sink.n; i++) {
                 V3 pa = sr_pts[i * 2 + 0], pb = sr_pts[i * 2 + 1];
@@ -890,7 +899,7 @@ __global__ void __launch_bounds__(32) k_test_motion(MtArgs m) {
                 float d = dot(n, pb);
                 float depth = dot(n, pa + recover_motion) - d;
                 if ((double)depth > (double)min_contact_depth + BPC_CMP_EPSILON) {
-                    recover_motion -= n * (depth - min_contact_depth) * 0.4f * 1.0f * 1.0f;
+                    recover_motion -= n * (depth - min_contact_depth) * 0.4f * prio[i] * inv_total_weight;
                 }
             }
             if (recover_motion == V3()) break;
@@ -1058,6 +1067,17 @@ extern "C" int bpc_bodies_test_motion(bpc_context *ctx, int n, const bpc_motion_
     m.except_keys = ctx->except_keys.p;
     m.n_except = ctx->n_except;
     m.n_bodies = ctx->n_bodies;
+    m.priority = nullptr;
+    if (!ctx->h_coll_priority.empty()) {
+        ctx->h_coll_priority.resize(ctx->n_bodies, 1.0f);
+        ctx->d_coll_priority.reserve(ctx->n_bodies, false, st);
+        if (!ctx->d_coll_priority.p) {
+            ctx->err = "bpc_bodies_test_motion: out of device memory";
+            return -1;
+        }
+        BPC_CHECK(cudaMemcpyAsync(ctx->d_coll_priority.p, ctx->h_coll_priority.data(), (size_t)ctx->n_bodies * sizeof(float), cudaMemcpyHostToDevice, st));
+        m.priority = ctx->d_coll_priority.p;
+    }
     BPC_CHECK(cudaMemcpyAsync((void *)m.params, params, (size_t)n * sizeof(bpc_motion_params), cudaMemcpyHostToDevice, st));
     k_test_motion<<<(n + 31) / 32, 32, 0, st>>>(m);
     BPC_CHECK(cudaGetLastError());

@@ -42,7 +42,7 @@ EXPORTS = [
     "bpc_pairs_read", "bpc_pairs_write", "bpc_set_solve_order", "bpc_sort_u64", "bpc_set_profiling", "bpc_get_stage_times",
     "bpc_space_set_active", "bpc_space_destroy", "bpc_bodies_create_slots", "bpc_bodies_destroy", "bpc_bodies_update",
     "bpc_bodies_set_state", "bpc_bodies_read_slots", "bpc_bodies_write_slots", "bpc_bodies_read_state", "bpc_reserve",
-    "bpc_shape_set_custom_bias", "bpc_bodies_closest_points", "bpc_bodies_set_same_object", "bpc_bodies_set_mass_override", "bpc_bodies_read_begin", "bpc_bodies_read_end", "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_joint_params_write", "bpc_joint_params_read", "bpc_test_segment_math", "bpc_bodies_set_exception",
+    "bpc_shape_set_custom_bias", "bpc_bodies_set_collision_priority", "bpc_bodies_closest_points", "bpc_bodies_set_same_object", "bpc_bodies_set_mass_override", "bpc_bodies_read_begin", "bpc_bodies_read_end", "bpc_joints_write", "bpc_joints_destroy", "bpc_joint_count", "bpc_joint_params_write", "bpc_joint_params_read", "bpc_test_segment_math", "bpc_bodies_set_exception",
     "bpc_bodies_set_max_contacts_reported", "bpc_body_read_contacts", "bpc_contacts_capacity", "bpc_contacts_read",
     "bpc_sort_u64_noalloc", "bpc_noalloc_last_error", "bpc_space_intersect_rays", "bpc_space_intersect_points", "bpc_space_intersect_shapes", "bpc_space_collide_shapes",
     "bpc_space_set_query_exclude", "bpc_space_rest_infos", "bpc_space_cast_motions",
@@ -100,6 +100,7 @@ def load_library(path=LIB_PATH):
     lib.bpc_joints_destroy.argtypes = [vp, ci, ci]
     lib.bpc_shape_set_custom_bias.argtypes = [vp, ci, ctypes.c_float]
     lib.bpc_bodies_read_begin.argtypes = [vp, ci, ci, ci, vp]
+    lib.bpc_bodies_set_collision_priority.argtypes = [vp, vp, ci, vp]
     lib.bpc_bodies_closest_points.argtypes = [vp, ci, vp, vp, vp]
     lib.bpc_bodies_set_same_object.argtypes = [vp, ci, ci, ci]
     lib.bpc_bodies_set_mass_override.argtypes = [vp, vp, ci, vp, vp]
@@ -356,6 +357,12 @@ class PhysicsServerCUDA:
         out = np.zeros((len(b), 3), np.float32)
         self._check(self.lib.bpc_bodies_closest_points(self.ctx, len(b), _ptr(b), _ptr(p), _ptr(out)))
         return out
+
+    def bodies_set_collision_priority(self, slots, priorities):
+        """body_set_collision_priority: the obstacles' weights when body_test_motion frees a stuck body."""
+        s = np.ascontiguousarray(slots, np.int32).reshape(-1)
+        v = np.ascontiguousarray(priorities, np.float32).reshape(len(s))
+        self._check(self.lib.bpc_bodies_set_collision_priority(self.ctx, _ptr(s), len(s), _ptr(v)))
 
     def bodies_set_same_object(self, a, b, same=True):
         """The two records are shapes of one object: they never enter the pair list."""

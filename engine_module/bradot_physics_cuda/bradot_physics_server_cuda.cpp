@@ -1075,6 +1075,25 @@ Variant BradotPhysicsServerCUDA::body_get_state(RID p_body, BodyState p_state) c
 	}
 }
 
+// body_set_collision_priority (bradot_physics_server_3d.cpp:611-623): what body_test_motion's recovery weighs its obstacles by
+void BradotPhysicsServerCUDA::body_set_collision_priority(RID p_body, real_t p_priority) {
+	Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL(body);
+	ERR_FAIL_COND_MSG(p_priority <= 0, "Priority must be greater than 0.");
+	body->collision_priority = p_priority;
+	if (body->slot >= 0) {
+		int32_t slot = body->slot;
+		float v = (float)p_priority;
+		ERR_FAIL_COND_MSG(bpc_bodies_set_collision_priority(ctx, &slot, 1, &v) < 0, bpc_last_error(ctx));
+	}
+}
+
+real_t BradotPhysicsServerCUDA::body_get_collision_priority(RID p_body) const {
+	const Body *body = body_owner.get_or_null(p_body);
+	ERR_FAIL_NULL_V(body, 0);
+	return body->collision_priority;
+}
+
 // body_set_ray_pickable (bradot_physics_server_3d.cpp:907-911): only rays cast with RayParameters::pick_ray pass such a body by
 void BradotPhysicsServerCUDA::body_set_ray_pickable(RID p_body, bool p_enable) {
 	Body *body = body_owner.get_or_null(p_body);
@@ -2691,6 +2710,12 @@ void BradotPhysicsServerCUDA::_flush_pending() {
 				if (b->max_contacts_reported > 0) {
 					int32_t slot = b->slot, cap = b->max_contacts_reported;
 					bpc_bodies_set_max_contacts_reported(ctx, &slot, 1, &cap);
+				}
+				const Body *owner = b->parent ? b->parent : b;
+				if (owner->collision_priority != 1.0) {
+					int32_t slot = b->slot;
+					float v = (float)owner->collision_priority;
+					bpc_bodies_set_collision_priority(ctx, &slot, 1, &v);
 				}
 				if (b->has_custom_inertia || b->has_custom_com) {
 					b->mass_override_dirty = true;

@@ -134,6 +134,7 @@ class BradotPhysicsServerCUDA : public PhysicsServer3D {
 		bool can_sleep = true;
 		bool ccd = false;
 		bool ray_pickable = true;
+		real_t collision_priority = 1.0;
 		// body_set_param(BODY_PARAM_INERTIA / BODY_PARAM_CENTER_OF_MASS): handed over with bpc_bodies_set_mass_override before the
 		// body is described (anew)
 		Vector3 custom_inertia, custom_com;
@@ -306,6 +307,8 @@ public:
 	virtual void shape_set_margin(RID p_shape, real_t p_margin) override;
 	virtual real_t shape_get_margin(RID p_shape) const override;
 	virtual void body_set_ray_pickable(RID p_body, bool p_enable) override;
+	virtual void body_set_collision_priority(RID p_body, real_t p_priority) override;
+	virtual real_t body_get_collision_priority(RID p_body) const override;
 	virtual void body_set_shape_disabled(RID p_body, int p_shape_idx, bool p_disabled) override;
 	virtual void body_set_user_flags(RID p_body, uint32_t p_flags) override;
 	virtual uint32_t body_get_user_flags(RID p_body) const override;

@@ -439,6 +439,7 @@ int main(int argc, char **argv) {
 				case 9: ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_CENTER_OF_MASS, Vector3(e.v[0], e.v[1], e.v[2])); break;
 				case 10: ps->body_reset_mass_properties(body); break;
 				case 11: ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_MASS, e.v[0]); break;
+				case 12: ps->body_set_collision_priority(body, e.v[0]); break;
 			}
 		}
 		for (size_t k = 0; k < kin_body.size(); k++) {

@@ -186,6 +186,9 @@ enum { BPC_STATE_TRANSFORM = 0, BPC_STATE_LINEAR_VELOCITY = 1, BPC_STATE_ANGULAR
 int bpc_bodies_set_state(bpc_context *ctx, int state, const int32_t *slots, int n, const float *values);
 /* Gather / scatter variants of the bulk I/O for a list of bodies (state sync of the active bodies only, forces of the pushed
  * bodies only): one staging copy and one kernel whatever n is. */
+/* body_set_collision_priority (P3D/bradot_physics_server_3d.cpp:611-616): how much of the push an obstacle gets when
+ * body_test_motion frees a stuck body (the only place the reference consults it, P3D/bradot_space_3d.cpp:748-762).  Default 1. */
+int bpc_bodies_set_collision_priority(bpc_context *ctx, const int32_t *slots, int n, const float *priorities);
 /* Two body records that are shapes of ONE object (the engine module's records for the further shapes of a static or kinematic
  * body): they never enter the pair list -- in the reference the shapes of one body are not paired with each other
  * (the pair test of its broadphase, `p_a == p_b`), whereas two separate kinematic bodies are.  same = 0 takes the mark back. */

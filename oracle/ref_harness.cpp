@@ -1363,6 +1363,9 @@ int main(int argc, char **argv) {
 				case 11:
 					ps->body_set_param(body, PhysicsServer3D::BODY_PARAM_MASS, e.v[0]);
 					break;
+				case 12:
+					ps->body_set_collision_priority(body, e.v[0]);
+					break;
 			}
 		}
 		drive_kinematic(d, w, s, hd.dt, true);

@@ -255,6 +255,43 @@ def test_kinematic_body_with_several_shapes(tmp_path):
     assert ref[1, 0] > 0.9          # the platform did travel
 
 
+def test_engine_module_collision_priority(tmp_path):
+    """body_set_collision_priority through the RID API (set on bodies that are already in the space): the module's body_test_motion
+    answers what bpc_bodies_test_motion answers on the same state with the same priorities -- and not what it answers without."""
+    if not os.path.exists(DEMO):
+        pytest.skip("engine_module/_build/engine_demo not built (needs the engine tree: python engine_module/build_demo.py)")
+    sc = scenes.mixed_pile(4, half=3.0)
+    nb = len(sc.bodies)
+    prio = np.ones(nb, np.float32)
+    prio[1::2] = 4.0
+    prio[0] = 0.2
+    events = [(2, int(b), 12, np.array([prio[b]] + [0] * 11, np.float32)) for b in range(nb) if prio[b] != 1.0]
+    steps = 80
+    path, evp = str(tmp_path / "scene.bscn"), str(tmp_path / "events.bin")
+    sc.write(path)
+    parity.write_events(evp, events)
+    r = subprocess.run([DEMO, path, str(steps), "--events", evp], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    mot = np.array(out["motions"], np.float64)
+    n = len(mot)
+    ps = server.PhysicsServerCUDA(0)
+    ps.load_scene(sc)
+    for _ in range(steps):
+        ps.step(sc.dt)
+    prm = np.zeros(n, server.MOTION_PARAMS_DT)
+    prm["body"] = np.arange(n)
+    prm["from"] = ps.bodies_read_state()[:n, 0:12]
+    prm["motion"], prm["margin"], prm["max_collisions"] = (0.05, -0.4, 0.0), 0.02, 4
+    plain = ps.bodies_test_motion(prm)
+    ps.bodies_set_collision_priority(np.arange(nb), prio)
+    mr = ps.bodies_test_motion(prm)
+    ps.finish()
+    assert np.array_equal(mot[:, 0] != 0, mr["collided"] != 0)
+    assert np.array_equal(mot[:, 3].astype(np.float32), mr["collision_safe_fraction"]) and np.array_equal(mot[:, 4:6].astype(np.float32), mr["travel"][:, 0:2])
+    assert not np.array_equal(plain["travel"], mr["travel"])            # the priorities do change the recovery
+
+
 def test_engine_module_areas_of_several_shapes(tmp_path):
     """area_add_shape beyond the first through the RID API: the module keeps each further shape as an area record of its own that
     shares the area's group (one override per body, events per shape through the area's own callback).  scenes.area_groups()

@@ -466,6 +466,50 @@ def test_body_test_motion_against_the_reference():
         ps.finish()
 
 
+def test_body_test_motion_weighs_obstacles_by_collision_priority():
+    """body_set_collision_priority (bradot_space_3d.cpp:748-762): the recovery step of body_test_motion pushes a stuck body away
+    from its obstacles in proportion to their priorities.  The settled pile of the test above with priority 4 on every other
+    body and 0.2 on the floor: the travel agrees with the reference running the same priorities (the bars of that test), and is
+    closer to it than what the same requests give when the priorities are left out."""
+    parity_needed()
+    sc = scenes.mixed_pile(5, half=3.5)
+    nb = len(sc.bodies)
+    prio = np.ones(nb, np.float32)
+    prio[1::2] = 4.0
+    prio[0] = 0.2
+    events = [(1, int(b), 12, np.array([prio[b]] + [0] * 11, np.float32)) for b in range(nb) if prio[b] != 1.0]
+    steps = 60
+    _, dump = parity.run_oracle(sc, steps, dump_from=0, dump_every=1, motions=True, events=events)
+    ps = parity.new_server(sc, dump)
+    worse = better = 0
+    for with_prio in (False, True):
+        if with_prio:
+            ps.bodies_set_collision_priority(np.arange(nb), prio)
+        errs = []
+        for k in (20, 40, 59):
+            parity.load_state(ps, dump, k)
+            q, ref = dump[("motion_queries", k)], dump[("motion_results", k)]
+            prm = np.zeros(len(q), server.MOTION_PARAMS_DT)
+            prm["body"], prm["from"], prm["motion"] = q[:, 0].astype(np.int32), q[:, 1:13], q[:, 13:16]
+            prm["margin"], prm["max_collisions"], prm["flags"] = q[:, 16], q[:, 17].astype(np.int32), q[:, 18].astype(np.uint32)
+            out = ps.bodies_test_motion(prm)
+            same = (out["collided"] > 0) == (ref[:, 0] > 0)
+            exact = (out["collision_safe_fraction"] == ref[:, 9]) & (out["collision_unsafe_fraction"] == ref[:, 10])
+            dtravel = np.abs(out["travel"] - ref[:, 2:5]).max(axis=1)
+            errs.append(dtravel)
+            if with_prio:
+                assert same.mean() > 0.98, (k, int((~same).sum()))
+                ok = same & exact
+                assert np.percentile(dtravel[ok], 50) == 0 and np.percentile(dtravel[ok], 95) < 5e-3, (k, float(np.percentile(dtravel[ok], 95)))
+        e = np.concatenate(errs)
+        if with_prio:
+            better = float(np.mean(e == 0))
+        else:
+            worse = float(np.mean(e == 0))
+    ps.finish()
+    assert better > worse + 0.1, (better, worse)       # share of requests whose travel is equal to the last bit
+
+
 def test_queries_against_a_triangle_mesh():
     """intersect_ray (BradotConcavePolygonShape3D::intersect_segment, bradot_shape_3d.cpp:1350-1423), intersect_shape, collide_shape
     and rest_info (solve_concave + the *_face routines) where the space holds triangle meshes: the terrain scene, the GPU using
