@@ -43,6 +43,7 @@ struct RayBest {
     bool collided;
     uint32_t body;
     V3 point, normal;
+    int face = -1;
 };
 
 // one candidate of the loop at bradot_space_3d.cpp:131-187; returns true when the search must stop (hit_from_inside)
@@ -81,6 +82,7 @@ __device__ inline bool q_ray_candidate(const QArgs &a, uint32_t j, V3 begin, V3 
             best.point = begin;
             best.normal = V3();
             best.body = j;
+            best.face = -1;
             best.collided = true;
             return true;
         }
@@ -95,6 +97,7 @@ __device__ inline bool q_ray_candidate(const QArgs &a, uint32_t j, V3 begin, V3 
             best.point = p;
             best.normal = normalized(xform_inv(inv_xform.b, h.normal));
             best.body = j;
+            best.face = h.face;
             best.collided = true;
         }
     }
@@ -134,6 +137,7 @@ __device__ inline bool q_ray_area(const QArgs &a, uint32_t ai, V3 begin, V3 end,
             best.point = p;
             best.normal = normalized(xform_inv(inv_xform.b, h.normal));
             best.body = (uint32_t)(-2 - (int)ai);
+            best.face = h.face;
             best.collided = true;
         }
     }
@@ -197,6 +201,7 @@ __global__ void __launch_bounds__(Q_THREADS) k_intersect_rays(QArgs a) {
     o.body = best.collided ? (int)best.body : -1;
     o.position[0] = best.point.x; o.position[1] = best.point.y; o.position[2] = best.point.z;
     o.normal[0] = best.normal.x; o.normal[1] = best.normal.y; o.normal[2] = best.normal.z;
+    o.face_index = best.collided ? best.face : -1;
     if (!best.collided) {
         o.position[0] = o.position[1] = o.position[2] = 0.f;
         o.normal[0] = o.normal[1] = o.normal[2] = 0.f;

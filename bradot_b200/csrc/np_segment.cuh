@@ -17,6 +17,7 @@ struct MeshPools {
 
 struct RayHit {
     V3 point, normal;
+    int face = -1; // triangle meshes: the index of the face hit (RayResult::face_index), else -1
 };
 
 // AABB::intersects_segment on a box given as (begin, end) per axis
@@ -317,6 +318,7 @@ __device__ inline bool q_mesh_segment(const MeshPools &a, const MeshRec &mesh, V
                         min_d = d;
                         h.point = res;
                         h.normal = normal;
+                        h.face = face_index;
                         collisions++;
                     }
                 }

@@ -69,7 +69,7 @@ MOTION_COLLISION_DT = np.dtype([("position", "<f4", 3), ("normal", "<f4", 3), ("
 MOTION_RESULT_DT = np.dtype([("collided", "<i4"), ("collision_count", "<i4"), ("travel", "<f4", 3), ("remainder", "<f4", 3), ("collision_depth", "<f4"),
                              ("collision_safe_fraction", "<f4"), ("collision_unsafe_fraction", "<f4"), ("collisions", MOTION_COLLISION_DT, 32)])
 REST_INFO_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("point", "<f4", 3), ("normal", "<f4", 3), ("linear_velocity", "<f4", 3)])
-RAY_RESULT_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("position", "<f4", 3), ("normal", "<f4", 3)])
+RAY_RESULT_DT = np.dtype([("hit", "<i4"), ("body", "<i4"), ("position", "<f4", 3), ("normal", "<f4", 3), ("face_index", "<i4")])
 
 
 def load_library(path=LIB_PATH):
@@ -450,6 +450,7 @@ class PhysicsServerCUDA:
         out = np.zeros(len(r), RAY_RESULT_DT)
         self._check(self.lib.bpc_space_intersect_rays(self.ctx, int(space), len(r), _ptr(r), ctypes.c_uint(collision_mask),
                                                       (1 if hit_from_inside else 0) | (2 if hit_back_faces else 0) | (4 if pick_ray else 0) | (8 if areas else 0) | (0 if bodies else 16), _ptr(out)))
+        self.last_ray_faces = out["face_index"].copy()      # RayResult::face_index of the rays just cast (-1: no mesh face)
         return out["hit"] != 0, out["body"].copy(), out["position"].copy(), out["normal"].copy()
 
     def intersect_points(self, points, space=0, collision_mask=0xFFFFFFFF, max_results=32, areas=False, bodies=True):

@@ -299,7 +299,7 @@ int BradotPhysicsDirectSpaceStateCUDA::intersect_rays_batch(const Vector<Vector3
 		r.collider_id = is_area ? server->area_of_handle[area_handle]->instance_id : server->body_of_slot[out[i].body]->instance_id;
 		r.collider = r.collider_id.is_valid() ? ObjectDB::get_instance(r.collider_id) : nullptr;
 		r.shape = is_area ? server->area_of_handle[area_handle]->shape_index : server->body_of_slot[out[i].body]->shape_index;
-		r.face_index = -1;
+		r.face_index = out[i].face_index;
 	}
 	return hits;
 }

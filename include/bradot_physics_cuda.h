@@ -336,12 +336,13 @@ int bpc_set_solve_order(bpc_context *ctx, int n, const int32_t *order);
  * one space -- closest hit along each segment, bodies whose collision layer meets collision_mask, a shape the ray starts
  * inside is ignored unless BPC_RAY_HIT_FROM_INSIDE.  from_to: n x (from xyz, to xyz), host; out: n records, host.
  * `body` is the body slot (what the engine module maps back to a RID / ObjectID), -1 for a miss.
- * Exclude lists: bpc_space_set_query_exclude below.  Not built: face_index. */
+ * Exclude lists: bpc_space_set_query_exclude below. */
 typedef struct bpc_ray_result {
     int32_t hit;
     int32_t body;
     float position[3];
     float normal[3];
+    int32_t face_index; /* RayResult::face_index: the face of a triangle mesh that was hit, else -1 */
 } bpc_ray_result;
 #define BPC_RAY_HIT_FROM_INSIDE 1
 #define BPC_QUERY_AREAS 8      /* collide_with_areas (rays and points): areas answer as well; an area's `body` is -2 - its index */

@@ -478,6 +478,7 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 	}
 	size_t n = rays.size() / 6;
 	std::vector<float> out(n * 8, 0.f);
+	std::vector<int32_t> ray_faces(n, -1); // RayResult::face_index of the plain rays
 	std::map<RID, int> area_index;
 	for (size_t i = 0; i < w.areas.size(); i++) {
 		area_index[w.areas[i]] = (int)i;
@@ -515,10 +516,16 @@ static void dump_rays(Dump &d, World &w, int step, const std::vector<float> &ray
 			out[i * 8 + 5] = rr.normal.x;
 			out[i * 8 + 6] = rr.normal.y;
 			out[i * 8 + 7] = rr.normal.z;
+			if (variant == 0) {
+				ray_faces[i] = rr.face_index;
+			}
 		}
 	}
 	static const char *names[4] = { "rays", "rays_pick", "rays_areas", "rays_areas_only" };
 	d.arr(names[variant], step, "f4", { (uint64_t)n, 8 }, out.data(), out.size() * 4);
+	if (variant == 0) {
+		d.arr("ray_faces", step, "i4", { (uint64_t)n }, ray_faces.data(), ray_faces.size() * 4);
+	}
 	}
 	// intersect_point (bradot_space_3d.cpp:62-107) at every ray's origin: count, then up to 8 body indices
 	std::vector<int32_t> pts(n * 9, -1);

@@ -537,6 +537,10 @@ def test_queries_against_a_triangle_mesh():
         sel = np.nonzero(both)[0][agree]
         assert np.max(np.abs(pos[sel] - ref[sel, 2:5])) < POS_TOL and np.max(np.abs(nrm[sel] - ref[sel, 5:8])) < NRM_TOL, k
         mesh_hits += int(np.isin(body[sel], (1, 2)).sum())
+        # RayResult::face_index: the face of the mesh that was hit (its index in the shape's face list), -1 for every other shape
+        faces, ref_faces = ps.last_ray_faces, dump[("ray_faces", k)]
+        on_mesh = np.isin(body[sel], (1, 2))
+        assert np.array_equal(faces[sel], ref_faces[sel]) and np.all(faces[sel][on_mesh] >= 0) and np.all(faces[sel][~on_mesh] == -1), k
         xf = dump[("shape_query_xf", k)]
         counts, bodies = ps.intersect_shapes(shape_of, xf, max_results=8)
         refq = dump[("shape_queries", k)]
