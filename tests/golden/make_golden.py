@@ -21,6 +21,11 @@ FIXTURES = {
     "mixed27": (lambda: scenes.mixed_pile(3, half=2.5), 64, 58),
     "chains12": (lambda: scenes.convex_chains(n_chains=4, chain_len=3, n_hulls=3), 84, 79),
     "freefall16": (lambda: scenes.free_fall(16), 6, 0),
+    # round 2: the joint types and body / shape parameters added then (each scene a handful of bodies)
+    "sliders4": (lambda: scenes.slider_rigs(4), 30, 27),
+    "sixdof4": (lambda: scenes.sixdof_rigs(4), 30, 27),
+    "cones2": (lambda: scenes.hanging_chains(2, 4, cone_twist=True), 30, 27),
+    "level2": (lambda: scenes.level_geometry(2), 40, 37),
 }
 
 

@@ -337,7 +337,7 @@ def test_teacher_forced_joint_chains():     # pin + hinge chains of convex hulls
     assert w["colliding"] > 0
 
 
-@pytest.mark.parametrize("name", ["pyramid21", "mixed27", "chains12"])
+@pytest.mark.parametrize("name", ["pyramid21", "mixed27", "chains12", "sliders4", "sixdof4", "cones2", "level2"])
 def test_teacher_forced_from_committed_golden_dump(name):
     """Same comparison as above, against the committed fixtures (outputs of the reference, tests/golden/):
     runs even where the oracle binary is not available."""
@@ -349,4 +349,4 @@ def test_teacher_forced_from_committed_golden_dump(name):
     dump = scenes.read_dump(os.path.join(parity.GOLDEN, name + ".bdmp"))
     w = parity.teacher_forced(make(), steps, list(range(first, steps)), dump=dump)
     assert w["contact"] < CONTACT_TOL and w["state"] < STATE_TOL, w
-    assert w["colliding"] > 0
+    assert w["colliding"] > 0 or name in ("sliders4", "sixdof4", "cones2")      # (the round-2 joint fixtures are joint-only islands)
